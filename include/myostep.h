@@ -1,0 +1,223 @@
+/* libmyostep.so -- C ABI of the B200-native batched musculoskeletal step.
+ *
+ * This is the drop-in boundary for the physics step the reference reaches through third-party code:
+ *   mjx.put_model / mjx.put_data / mjx.step / mjx.get_data   (reference: myosuite/mjx/play.py:10-11,41,47,49)
+ *   brax pipeline_init / pipeline_step                       (reference: myosuite/mjx/myodm_v0.py:159,287)
+ *   dm_control Physics.step(n) -> n x mj_step, sim.forward() (reference: myosuite/physics/mj_sim_scene.py:55,
+ *                                                             myosuite/robot/robot.py:880-882,976-979)
+ * Plain pointers and sizes only; no torch / jax types.  All device work is enqueued on the caller's CUDA
+ * stream (passed as void* = cudaStream_t); nothing here synchronises unless stated.
+ *
+ * Batched layout: every per-world field is a dense row-major array with the WORLD AXIS LEADING
+ * ([nworld][k...]), i.e. exactly the layout of a vmapped mjx.Data pytree leaf.  One warp owns one world,
+ * so each warp reads and writes contiguous runs.
+ */
+#ifndef MYOSTEP_H_
+#define MYOSTEP_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MYO_NPRM 10      /* mjNGAIN / mjNBIAS / mjNDYN */
+#define MYO_NEQDATA 11   /* mjNEQDATA */
+#define MYO_NIMP 5
+#define MYO_NREF 2
+
+/* mjModel-shaped host arrays (float64 / int32, row-major, field names and enum values of MuJoCo 3.2.8's
+ * mjModel).  Filled by mjx.put_model from our MJCF compiler or from a real mujoco.MjModel. */
+typedef struct myo_model_desc {
+  /* sizes */
+  int32_t nq, nv, nu, na, nbody, njnt, ngeom, nsite, ntendon, nwrap, neq, npair, nexclude, nM;
+  /* mjOption */
+  int32_t opt_iterations, opt_ls_iterations, opt_disableflags, opt_cone, opt_solver, opt_integrator;
+  double opt_timestep, opt_tolerance, opt_ls_tolerance, opt_impratio;
+  double opt_gravity[3];
+  double stat_meaninertia;
+  /* bodies */
+  const int32_t *body_parentid, *body_rootid, *body_weldid, *body_jntnum, *body_jntadr, *body_dofnum, *body_dofadr,
+      *body_geomnum, *body_geomadr;
+  const double *body_pos, *body_quat, *body_ipos, *body_iquat, *body_mass, *body_subtreemass, *body_inertia,
+      *body_invweight0;
+  /* joints and dofs */
+  const int32_t *jnt_type, *jnt_qposadr, *jnt_dofadr, *jnt_bodyid, *jnt_limited;
+  const double *jnt_pos, *jnt_axis, *jnt_stiffness, *jnt_range, *jnt_margin, *jnt_solref, *jnt_solimp;
+  const double *qpos0, *qpos_spring;
+  const int32_t *dof_bodyid, *dof_jntid, *dof_parentid, *dof_Madr;
+  const double *dof_armature, *dof_damping, *dof_invweight0;
+  /* geoms and sites */
+  const int32_t *geom_type, *geom_contype, *geom_conaffinity, *geom_condim, *geom_bodyid, *geom_priority;
+  const double *geom_size, *geom_rbound, *geom_pos, *geom_quat, *geom_friction, *geom_solmix, *geom_solref,
+      *geom_solimp, *geom_margin, *geom_gap;
+  const int32_t *site_bodyid;
+  const double *site_pos, *site_quat;
+  /* tendons */
+  const int32_t *tendon_adr, *tendon_num, *tendon_limited;
+  const double *tendon_range, *tendon_margin, *tendon_stiffness, *tendon_damping, *tendon_lengthspring,
+      *tendon_solref_lim, *tendon_solimp_lim, *tendon_invweight0;
+  const int32_t *wrap_type, *wrap_objid;
+  const double *wrap_prm;
+  /* actuators */
+  const int32_t *actuator_trntype, *actuator_trnid, *actuator_dyntype, *actuator_gaintype, *actuator_biastype,
+      *actuator_ctrllimited, *actuator_forcelimited, *actuator_actlimited, *actuator_actadr;
+  const double *actuator_dynprm, *actuator_gainprm, *actuator_biasprm, *actuator_ctrlrange, *actuator_forcerange,
+      *actuator_actrange, *actuator_lengthrange, *actuator_gear, *actuator_acc0;
+  /* equality constraints (joint type only) */
+  const int32_t *eq_type, *eq_obj1id, *eq_obj2id, *eq_active0;
+  const double *eq_data, *eq_solref, *eq_solimp;
+  /* explicit contact pairs and excludes */
+  const int32_t *pair_dim, *pair_geom1, *pair_geom2, *exclude_signature;
+  const double *pair_solref, *pair_solimp, *pair_margin, *pair_gap, *pair_friction;
+} myo_model_desc;
+
+/* status codes */
+enum {
+  MYO_OK = 0,
+  MYO_ERR_ARG = -1,          /* bad argument / unknown field / size mismatch */
+  MYO_ERR_UNSUPPORTED = -2,  /* model uses a feature outside the supported subset (raised at model create) */
+  MYO_ERR_CUDA = -3,         /* CUDA runtime error; no CPU fallback exists */
+  MYO_ERR_UNBOUND = -4       /* a required state field has no bound device buffer */
+};
+
+/* per-world status bits written by the step kernel into the `status` field */
+enum {
+  MYO_WORLD_BADQACC = 1,     /* NaN/Inf or huge qacc: world was reset to qpos0 (mj_checkAcc rule) */
+  MYO_WORLD_NCON_OVERFLOW = 2,
+  MYO_WORLD_NEFC_OVERFLOW = 4,
+  MYO_WORLD_SOLVER_MAXITER = 8,
+  MYO_WORLD_BADQPOS = 16,
+  MYO_WORLD_BADQVEL = 32
+};
+
+/* Batched per-world fields.  State fields are read and written in place by myo_step; the others are
+ * outputs (mjData names).  Shapes are per world; dtype float32 unless noted. */
+typedef enum myo_field {
+  /* state */
+  MYO_F_QPOS = 0,        /* [nq] */
+  MYO_F_QVEL,            /* [nv] */
+  MYO_F_ACT,             /* [na] */
+  MYO_F_CTRL,            /* [nu]   input */
+  MYO_F_TIME,            /* [1] */
+  MYO_F_QACC_WARMSTART,  /* [nv] */
+  /* outputs */
+  MYO_F_QACC,            /* [nv] */
+  MYO_F_QACC_SMOOTH,     /* [nv] */
+  MYO_F_ACT_DOT,         /* [na] */
+  MYO_F_XPOS,            /* [nbody,3] */
+  MYO_F_XQUAT,           /* [nbody,4] */
+  MYO_F_XMAT,            /* [nbody,9] */
+  MYO_F_XIPOS,           /* [nbody,3] */
+  MYO_F_XIMAT,           /* [nbody,9] */
+  MYO_F_XANCHOR,         /* [njnt,3] */
+  MYO_F_XAXIS,           /* [njnt,3] */
+  MYO_F_GEOM_XPOS,       /* [ngeom,3] */
+  MYO_F_GEOM_XMAT,       /* [ngeom,9] */
+  MYO_F_SITE_XPOS,       /* [nsite,3] */
+  MYO_F_SITE_XMAT,       /* [nsite,9] */
+  MYO_F_SUBTREE_COM,     /* [nbody,3] */
+  MYO_F_CINERT,          /* [nbody,10] */
+  MYO_F_CRB,             /* [nbody,10] */
+  MYO_F_CDOF,            /* [nv,6] */
+  MYO_F_CDOF_DOT,        /* [nv,6] */
+  MYO_F_CVEL,            /* [nbody,6] */
+  MYO_F_TEN_LENGTH,      /* [ntendon] */
+  MYO_F_TEN_VELOCITY,    /* [ntendon] */
+  MYO_F_TEN_J,           /* [ntendon,nv] */
+  MYO_F_TEN_WRAPADR,     /* [ntendon] int32 */
+  MYO_F_TEN_WRAPNUM,     /* [ntendon] int32 */
+  MYO_F_WRAP_OBJ,        /* [nwrap,2] int32 */
+  MYO_F_WRAP_XPOS,       /* [nwrap,6] */
+  MYO_F_ACTUATOR_LENGTH,   /* [nu] */
+  MYO_F_ACTUATOR_VELOCITY, /* [nu] */
+  MYO_F_ACTUATOR_MOMENT,   /* [nu,nv] */
+  MYO_F_ACTUATOR_FORCE,    /* [nu] */
+  MYO_F_QM,              /* [nv,nv] dense symmetric (MJX layout for nv<60) */
+  MYO_F_QLD,             /* [nv,nv] dense: strict lower part = L (unit, L^T D L), diagonal = D */
+  MYO_F_QLDIAGINV,       /* [nv] */
+  MYO_F_QFRC_BIAS,       /* [nv] */
+  MYO_F_QFRC_PASSIVE,    /* [nv] */
+  MYO_F_QFRC_SPRING,     /* [nv] */
+  MYO_F_QFRC_DAMPER,     /* [nv] */
+  MYO_F_QFRC_ACTUATOR,   /* [nv] */
+  MYO_F_QFRC_SMOOTH,     /* [nv] */
+  MYO_F_QFRC_CONSTRAINT, /* [nv] */
+  MYO_F_QFRC_INVERSE,    /* [nv] */
+  /* constraints and contacts (padded to njmax / nconmax rows per world) */
+  MYO_F_NCON,            /* [1] int32 */
+  MYO_F_NEFC,            /* [1] int32 */
+  MYO_F_CONTACT_GEOM,    /* [nconmax,2] int32   (geom1, geom2) */
+  MYO_F_CONTACT_DIM,     /* [nconmax] int32 */
+  MYO_F_CONTACT_EFC_ADDRESS, /* [nconmax] int32 */
+  MYO_F_CONTACT_DIST,    /* [nconmax] */
+  MYO_F_CONTACT_POS,     /* [nconmax,3] */
+  MYO_F_CONTACT_FRAME,   /* [nconmax,9] */
+  MYO_F_CONTACT_INCLUDEMARGIN, /* [nconmax] */
+  MYO_F_CONTACT_FRICTION,/* [nconmax,5] */
+  MYO_F_CONTACT_SOLREF,  /* [nconmax,2] */
+  MYO_F_CONTACT_SOLIMP,  /* [nconmax,5] */
+  MYO_F_EFC_J,           /* [njmax,nv] */
+  MYO_F_EFC_POS,         /* [njmax] */
+  MYO_F_EFC_MARGIN,      /* [njmax] */
+  MYO_F_EFC_D,           /* [njmax] */
+  MYO_F_EFC_AREF,        /* [njmax] */
+  MYO_F_EFC_FORCE,       /* [njmax] */
+  MYO_F_EFC_TYPE,        /* [njmax] int32 (mjtConstraint) */
+  MYO_F_SOLVER_NITER,    /* [1] int32 */
+  MYO_F_STATUS,          /* [1] int32, MYO_WORLD_* bits, sticky until myo_reset */
+  MYO_F_COUNT
+} myo_field;
+
+typedef struct myo_model myo_model;   /* device-resident compiled model (immutable) */
+typedef struct myo_batch myo_batch;   /* nworld worlds of one model on one device */
+
+/* mjx.put_model: copy + preprocess the model onto `device`.  Fails with MYO_ERR_UNSUPPORTED like MJX's
+ * put_model raises NotImplementedError (reference: myosuite/mjx/play.py:10). */
+int myo_model_create(const myo_model_desc *desc, int device, myo_model **out);
+void myo_model_destroy(myo_model *m);
+
+/* Batch of `nworld` worlds; nconmax / njmax are per-world capacities (0 = model-derived default). */
+int myo_batch_create(const myo_model *m, int nworld, int nconmax, int njmax, myo_batch **out);
+void myo_batch_destroy(myo_batch *b);
+int myo_batch_nconmax(const myo_batch *b);
+int myo_batch_njmax(const myo_batch *b);
+
+/* Per-world element count / element size of a field for this batch (0 elements = field absent for the model). */
+int64_t myo_field_count(const myo_batch *b, int field);
+int myo_field_itemsize(int field);
+const char *myo_field_name(int field);
+
+/* Bind a caller-owned device buffer (e.g. a DLPack-exported torch / jax array) of
+ * nworld * myo_field_count(field) elements to `field`; zero-copy, the library never frees it.
+ * dev_ptr == NULL unbinds (an unbound output field is simply not materialised). */
+int myo_batch_bind(myo_batch *b, int field, void *dev_ptr, int64_t nbytes);
+
+/* mj_forward on every world (reference: sim.forward() at myosuite/robot/robot.py:979; brax pipeline_init at
+ * myosuite/mjx/myodm_v0.py:159): all outputs from the bound state, state not advanced. */
+int myo_forward(myo_batch *b, void *cuda_stream);
+
+/* nsubsteps x mj_step on every world with ctrl held (reference: jit_step at myosuite/mjx/play.py:47;
+ * sim.advance(substeps=n_frames) at myosuite/robot/robot.py:880-882; pipeline_step at myodm_v0.py:287).
+ * Output fields describe the last substep's forward pass, as mjData does after mj_step. */
+int myo_step(myo_batch *b, int nsubsteps, void *cuda_stream);
+
+/* mj_resetData + mj_forward on worlds whose mask entry is non-zero (NULL = all): qpos=qpos0, qvel=act=0,
+ * time=0, warmstart=0, status=0 (reference: myosuite/robot/robot.py:976-979). world_mask is int32[nworld] on device. */
+int myo_reset(myo_batch *b, const int32_t *world_mask_dev, void *cuda_stream);
+
+/* Host-buffer convenience used by the end-to-end path: H2D of qpos/qvel/act/ctrl (any may be NULL), step,
+ * D2H of qpos/qvel/act.  Pinned host memory makes the copies asynchronous; synchronises the stream at the end. */
+int myo_step_host(myo_batch *b, int nsubsteps, const float *qpos, const float *qvel, const float *act,
+                  const float *ctrl, float *qpos_out, float *qvel_out, float *act_out, void *cuda_stream);
+
+/* number of kernels launched by this library since load (for bench.py's gpu_launches) */
+int64_t myo_launch_count(void);
+
+/* thread-local message for the last non-zero status */
+const char *myo_last_error(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MYOSTEP_H_ */

@@ -165,8 +165,8 @@ def wrap_geom(x0, x1, gpos, gmat, radius, wtype, side):
     if side is not None:
         s = gmat.T @ (side - gpos)
         sd = np.array([s @ ax0, s @ ax1])
-        # "inside" when the side site lies within the wrap radius (sphere: 3-D, cylinder: in the cross-section)
-        inside = (np.linalg.norm(s) if wtype == WRAP_SPHERE else np.linalg.norm(s[:2])) < radius
+        # "inside" when the side site lies within the wrap radius (3-D norm in the geom frame, both wrap types)
+        inside = np.linalg.norm(s) < radius
         sd = radius * sd / max(np.linalg.norm(sd), MINVAL)
     r = wrap_inside(d0, d1, radius) if inside else wrap_circle(d0, d1, sd, radius)
     if r is None:
