@@ -186,6 +186,7 @@ int myo_batch_njmax(const myo_batch *b);
 /* Per-world element count / element size of a field for this batch (0 elements = field absent for the model). */
 int64_t myo_field_count(const myo_batch *b, int field);
 int myo_field_itemsize(int field);
+int myo_field_is_int(int field);   /* 1: int32 elements, 0: float32 */
 const char *myo_field_name(int field);
 
 /* Bind a caller-owned device buffer (e.g. a DLPack-exported torch / jax array) of

@@ -1,0 +1,212 @@
+// C ABI of libmyostep.so (see include/myostep.h).  Thin: argument checks, buffer binding, kernel launch.
+// There is NO CPU fallback: every entry that computes needs a CUDA device and fails with MYO_ERR_CUDA without one.
+#include <cuda_runtime.h>
+
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "devmodel.h"
+#include "internal.h"
+
+int64_t myo_launch_counter();
+
+struct myo_model {
+  DevModel D;
+  SmemLayout L;
+  std::vector<void*> owned;
+  int device;
+};
+struct myo_batch {
+  const myo_model* model;
+  DevModel D;   // copy with this batch's nconmax / njmax
+  SmemLayout L;
+  FieldPtrs F;
+  int nworld;
+  std::vector<void*> owned;
+};
+
+namespace {
+thread_local std::string g_err;
+int fail(int code, const std::string& msg) { g_err = msg; return code; }
+
+const char* kFieldNames[MYO_F_COUNT] = {
+    "qpos", "qvel", "act", "ctrl", "time", "qacc_warmstart", "qacc", "qacc_smooth", "act_dot", "xpos", "xquat", "xmat", "xipos",
+    "ximat", "xanchor", "xaxis", "geom_xpos", "geom_xmat", "site_xpos", "site_xmat", "subtree_com", "cinert", "crb", "cdof",
+    "cdof_dot", "cvel", "ten_length", "ten_velocity", "ten_J", "ten_wrapadr", "ten_wrapnum", "wrap_obj", "wrap_xpos",
+    "actuator_length", "actuator_velocity", "actuator_moment", "actuator_force", "qM", "qLD", "qLDiagInv", "qfrc_bias",
+    "qfrc_passive", "qfrc_spring", "qfrc_damper", "qfrc_actuator", "qfrc_smooth", "qfrc_constraint", "qfrc_inverse", "ncon",
+    "nefc", "contact_geom", "contact_dim", "contact_efc_address", "contact_dist", "contact_pos", "contact_frame",
+    "contact_includemargin", "contact_friction", "contact_solref", "contact_solimp", "efc_J", "efc_pos", "efc_margin", "efc_D",
+    "efc_aref", "efc_force", "efc_type", "solver_niter", "status"};
+
+bool isIntField(int f) {
+  switch (f) {
+    case MYO_F_TEN_WRAPADR: case MYO_F_TEN_WRAPNUM: case MYO_F_WRAP_OBJ: case MYO_F_NCON: case MYO_F_NEFC: case MYO_F_CONTACT_GEOM:
+    case MYO_F_CONTACT_DIM: case MYO_F_CONTACT_EFC_ADDRESS: case MYO_F_EFC_TYPE: case MYO_F_SOLVER_NITER: case MYO_F_STATUS: return true;
+    default: return false;
+  }
+}
+int64_t fieldCount(const DevModel& D, int f) {
+  const int64_t nv = D.nv, nb = D.nbody, nc = D.nconmax, nj = D.njmax;
+  switch (f) {
+    case MYO_F_QPOS: return D.nq;
+    case MYO_F_QVEL: case MYO_F_QACC_WARMSTART: case MYO_F_QACC: case MYO_F_QACC_SMOOTH: case MYO_F_QLDIAGINV: case MYO_F_QFRC_BIAS:
+    case MYO_F_QFRC_PASSIVE: case MYO_F_QFRC_SPRING: case MYO_F_QFRC_DAMPER: case MYO_F_QFRC_ACTUATOR: case MYO_F_QFRC_SMOOTH:
+    case MYO_F_QFRC_CONSTRAINT: case MYO_F_QFRC_INVERSE: return nv;
+    case MYO_F_ACT: case MYO_F_ACT_DOT: return D.na;
+    case MYO_F_CTRL: case MYO_F_ACTUATOR_LENGTH: case MYO_F_ACTUATOR_VELOCITY: case MYO_F_ACTUATOR_FORCE: return D.nu;
+    case MYO_F_TIME: case MYO_F_NCON: case MYO_F_NEFC: case MYO_F_SOLVER_NITER: case MYO_F_STATUS: return 1;
+    case MYO_F_XPOS: case MYO_F_XIPOS: case MYO_F_SUBTREE_COM: return 3 * nb;
+    case MYO_F_XQUAT: return 4 * nb;
+    case MYO_F_XMAT: case MYO_F_XIMAT: return 9 * nb;
+    case MYO_F_XANCHOR: case MYO_F_XAXIS: return 3 * (int64_t)D.njnt;
+    case MYO_F_GEOM_XPOS: return 3 * (int64_t)D.ngeom;
+    case MYO_F_GEOM_XMAT: return 9 * (int64_t)D.ngeom;
+    case MYO_F_SITE_XPOS: return 3 * (int64_t)D.nsite;
+    case MYO_F_SITE_XMAT: return 9 * (int64_t)D.nsite;
+    case MYO_F_CINERT: case MYO_F_CRB: return 10 * nb;
+    case MYO_F_CDOF: case MYO_F_CDOF_DOT: return 6 * nv;
+    case MYO_F_CVEL: return 6 * nb;
+    case MYO_F_TEN_LENGTH: case MYO_F_TEN_VELOCITY: return D.nten;
+    case MYO_F_TEN_J: return (int64_t)D.nten * nv;
+    case MYO_F_TEN_WRAPADR: case MYO_F_TEN_WRAPNUM: case MYO_F_WRAP_OBJ: case MYO_F_WRAP_XPOS: return 0;  // render-only path points: not materialised
+    case MYO_F_ACTUATOR_MOMENT: return (int64_t)D.nu * nv;
+    case MYO_F_QM: case MYO_F_QLD: return nv * nv;
+    case MYO_F_CONTACT_GEOM: case MYO_F_CONTACT_SOLREF: return 2 * nc;
+    case MYO_F_CONTACT_DIM: case MYO_F_CONTACT_EFC_ADDRESS: case MYO_F_CONTACT_DIST: case MYO_F_CONTACT_INCLUDEMARGIN: return nc;
+    case MYO_F_CONTACT_POS: return 3 * nc;
+    case MYO_F_CONTACT_FRAME: return 9 * nc;
+    case MYO_F_CONTACT_FRICTION: case MYO_F_CONTACT_SOLIMP: return 5 * nc;
+    case MYO_F_EFC_J: return nj * nv;
+    case MYO_F_EFC_POS: case MYO_F_EFC_MARGIN: case MYO_F_EFC_D: case MYO_F_EFC_AREF: case MYO_F_EFC_FORCE: case MYO_F_EFC_TYPE: return nj;
+    default: return 0;
+  }
+}
+const int kStateFields[] = {MYO_F_QPOS, MYO_F_QVEL, MYO_F_ACT, MYO_F_CTRL, MYO_F_TIME, MYO_F_QACC_WARMSTART, MYO_F_STATUS};
+
+int checkReady(myo_batch* b) {
+  if (!b) return fail(MYO_ERR_ARG, "null batch");
+  for (int f : kStateFields)
+    if (!b->F.p[f]) return fail(MYO_ERR_UNBOUND, std::string("state field not bound: ") + kFieldNames[f]);
+  if (cudaSetDevice(b->model->device) != cudaSuccess) return fail(MYO_ERR_CUDA, "cudaSetDevice failed");
+  return MYO_OK;
+}
+}  // namespace
+
+extern "C" {
+
+const char* myo_last_error(void) { return g_err.c_str(); }
+int64_t myo_launch_count(void) { return myo_launch_counter(); }
+const char* myo_field_name(int field) { return (field >= 0 && field < MYO_F_COUNT) ? kFieldNames[field] : ""; }
+int myo_field_itemsize(int field) { (void)field; return 4; }
+int myo_field_is_int(int field) { return isIntField(field) ? 1 : 0; }
+
+int myo_model_create(const myo_model_desc* desc, int device, myo_model** out) {
+  if (!desc || !out) return fail(MYO_ERR_ARG, "null argument");
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+    return fail(MYO_ERR_CUDA, "no CUDA device: libmyostep has no CPU fallback");
+  if (device < 0 || device >= ndev || cudaSetDevice(device) != cudaSuccess) return fail(MYO_ERR_CUDA, "bad CUDA device index");
+  myo_model* m = new myo_model();
+  m->device = device;
+  try {
+    myo_build_plan(*desc, 0, 0, m->D, m->L, m->owned);
+  } catch (const std::string& e) {
+    for (void* p : m->owned) cudaFree(p);
+    delete m;
+    const bool cuda = e.find("cuda") != std::string::npos;
+    return fail(cuda ? MYO_ERR_CUDA : MYO_ERR_UNSUPPORTED, e);
+  }
+  *out = m;
+  return MYO_OK;
+}
+void myo_model_destroy(myo_model* m) {
+  if (!m) return;
+  cudaSetDevice(m->device);
+  for (void* p : m->owned) cudaFree(p);
+  delete m;
+}
+
+int myo_batch_create(const myo_model* m, int nworld, int nconmax, int njmax, myo_batch** out) {
+  if (!m || !out || nworld <= 0) return fail(MYO_ERR_ARG, "bad argument");
+  if (cudaSetDevice(m->device) != cudaSuccess) return fail(MYO_ERR_CUDA, "cudaSetDevice failed");
+  myo_batch* b = new myo_batch();
+  b->model = m; b->D = m->D; b->nworld = nworld;
+  memset(&b->F, 0, sizeof(b->F));
+  try {
+    myo_make_layout(b->D, nconmax, njmax, b->L);
+  } catch (const std::string& e) { delete b; return fail(MYO_ERR_ARG, e); }
+  if (myo_kernel_smem_bytes(b->L) > 220 * 1024) { delete b; return fail(MYO_ERR_UNSUPPORTED, "model does not fit the per-world shared-memory arena"); }
+  // library-owned default state buffers (bind overrides them)
+  for (int f : kStateFields) {
+    void* p = nullptr;
+    size_t n = (size_t)nworld * std::max<int64_t>(1, fieldCount(b->D, f)) * 4;
+    if (cudaMalloc(&p, n) != cudaSuccess || cudaMemset(p, 0, n) != cudaSuccess) { myo_batch_destroy(b); return fail(MYO_ERR_CUDA, "cudaMalloc failed"); }
+    b->owned.push_back(p); b->F.p[f] = p;
+  }
+  *out = b;
+  return MYO_OK;
+}
+void myo_batch_destroy(myo_batch* b) {
+  if (!b) return;
+  cudaSetDevice(b->model->device);
+  for (void* p : b->owned) cudaFree(p);
+  delete b;
+}
+int myo_batch_nconmax(const myo_batch* b) { return b ? b->D.nconmax : 0; }
+int myo_batch_njmax(const myo_batch* b) { return b ? b->D.njmax : 0; }
+int64_t myo_field_count(const myo_batch* b, int field) { return (b && field >= 0 && field < MYO_F_COUNT) ? fieldCount(b->D, field) : 0; }
+
+int myo_batch_bind(myo_batch* b, int field, void* dev_ptr, int64_t nbytes) {
+  if (!b || field < 0 || field >= MYO_F_COUNT) return fail(MYO_ERR_ARG, "bad field id");
+  if (dev_ptr) {
+    const int64_t need = (int64_t)b->nworld * fieldCount(b->D, field) * 4;
+    if (need == 0) return fail(MYO_ERR_ARG, std::string("field is empty for this model: ") + kFieldNames[field]);
+    if (nbytes != need) return fail(MYO_ERR_ARG, std::string("size mismatch binding ") + kFieldNames[field]);
+    if (((uintptr_t)dev_ptr & 3) != 0) return fail(MYO_ERR_ARG, "buffer must be 4-byte aligned");
+  } else {
+    for (int f : kStateFields) if (f == field) return fail(MYO_ERR_ARG, "state fields cannot be unbound");
+  }
+  b->F.p[field] = dev_ptr;
+  return MYO_OK;
+}
+
+static int launch(myo_batch* b, int nsub, int forward_only, const int32_t* mask, int do_reset, void* stream) {
+  int rc = checkReady(b);
+  if (rc) return rc;
+  if (myo_launch_step(b->D, b->L, b->F, b->nworld, nsub, forward_only, mask, do_reset, stream) != 0)
+    return fail(MYO_ERR_CUDA, std::string("kernel launch failed: ") + cudaGetErrorString(cudaGetLastError()));
+  return MYO_OK;
+}
+int myo_forward(myo_batch* b, void* stream) { return launch(b, 0, 1, nullptr, 0, stream); }
+int myo_step(myo_batch* b, int nsubsteps, void* stream) {
+  if (nsubsteps < 1) return fail(MYO_ERR_ARG, "nsubsteps must be >= 1");
+  return launch(b, nsubsteps, 0, nullptr, 0, stream);
+}
+int myo_reset(myo_batch* b, const int32_t* world_mask_dev, void* stream) { return launch(b, 0, 1, world_mask_dev, 1, stream); }
+
+int myo_step_host(myo_batch* b, int nsubsteps, const float* qpos, const float* qvel, const float* act, const float* ctrl,
+                  float* qpos_out, float* qvel_out, float* act_out, void* stream) {
+  int rc = checkReady(b);
+  if (rc) return rc;
+  cudaStream_t s = (cudaStream_t)stream;
+  const size_t n = b->nworld;
+  const DevModel& D = b->D;
+  bool ok = true;
+  if (qpos) ok &= cudaMemcpyAsync(b->F.p[MYO_F_QPOS], qpos, n * D.nq * 4, cudaMemcpyHostToDevice, s) == cudaSuccess;
+  if (qvel) ok &= cudaMemcpyAsync(b->F.p[MYO_F_QVEL], qvel, n * D.nv * 4, cudaMemcpyHostToDevice, s) == cudaSuccess;
+  if (act && D.na) ok &= cudaMemcpyAsync(b->F.p[MYO_F_ACT], act, n * D.na * 4, cudaMemcpyHostToDevice, s) == cudaSuccess;
+  if (ctrl && D.nu) ok &= cudaMemcpyAsync(b->F.p[MYO_F_CTRL], ctrl, n * D.nu * 4, cudaMemcpyHostToDevice, s) == cudaSuccess;
+  if (!ok) return fail(MYO_ERR_CUDA, "host-to-device copy failed");
+  rc = myo_step(b, nsubsteps, stream);
+  if (rc) return rc;
+  if (qpos_out) ok &= cudaMemcpyAsync(qpos_out, b->F.p[MYO_F_QPOS], n * D.nq * 4, cudaMemcpyDeviceToHost, s) == cudaSuccess;
+  if (qvel_out) ok &= cudaMemcpyAsync(qvel_out, b->F.p[MYO_F_QVEL], n * D.nv * 4, cudaMemcpyDeviceToHost, s) == cudaSuccess;
+  if (act_out && D.na) ok &= cudaMemcpyAsync(act_out, b->F.p[MYO_F_ACT], n * D.na * 4, cudaMemcpyDeviceToHost, s) == cudaSuccess;
+  if (!ok || cudaStreamSynchronize(s) != cudaSuccess) return fail(MYO_ERR_CUDA, std::string("device-to-host copy failed: ") + cudaGetErrorString(cudaGetLastError()));
+  return MYO_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,1668 @@
+// Fused batched mj_step for sm_100a: ONE WARP PER WORLD, whole step (nsub substeps) in one launch, all
+// intermediates in a per-warp shared-memory arena, state read once and written once per launch.
+//
+// What it replaces (third-party code the reference calls; see include/myostep.h for the call sites):
+//   mj_kinematics, mj_comPos, mj_tendon (+mju_wrap), mj_crb, mj_factorM, mj_collision, mj_makeConstraint,
+//   mj_transmission, mj_fwdVelocity (comVel, passive, rne), mj_fwdActuation (muscle dynamics / gain / bias),
+//   mj_fwdAcceleration, mj_fwdConstraint (Newton), mj_Euler.
+// Global memory: every field is [nworld][k] (world-major, MJX batch layout); a warp reads/writes contiguous runs.
+#include <cuda_runtime.h>
+#include <math_constants.h>
+
+#include "devmodel.h"
+#include "internal.h"
+
+#define MINVAL 1e-15f
+#define FULLMASK 0xffffffffu
+
+namespace {
+
+enum { JNT_FREE = 0, JNT_BALL = 1, JNT_SLIDE = 2, JNT_HINGE = 3 };
+enum { G_PLANE = 0, G_HFIELD, G_SPHERE, G_CAPSULE, G_ELLIPSOID, G_CYLINDER, G_BOX, G_MESH };
+enum { DYN_NONE = 0, DYN_INTEGRATOR, DYN_FILTER, DYN_FILTEREXACT, DYN_MUSCLE };
+enum { GAIN_FIXED = 0, GAIN_AFFINE, GAIN_MUSCLE };
+enum { BIAS_NONE = 0, BIAS_AFFINE, BIAS_MUSCLE };
+enum { DSBL_CONSTRAINT = 1 << 0, DSBL_EQUALITY = 1 << 1, DSBL_LIMIT = 1 << 3, DSBL_CONTACT = 1 << 4, DSBL_PASSIVE = 1 << 5,
+       DSBL_GRAVITY = 1 << 6, DSBL_CLAMPCTRL = 1 << 7, DSBL_WARMSTART = 1 << 8, DSBL_ACTUATION = 1 << 10 };
+enum { ROW_EQ = 0, ROW_LIMJ = 1, ROW_LIMT = 2, ROW_CON = 3 };
+
+// ------------------------------------------------------------------------------------------ small math
+struct f3 { float x, y, z; };
+__device__ __forceinline__ f3 mk3(float x, float y, float z) { f3 r; r.x = x; r.y = y; r.z = z; return r; }
+__device__ __forceinline__ f3 operator+(f3 a, f3 b) { return mk3(a.x + b.x, a.y + b.y, a.z + b.z); }
+__device__ __forceinline__ f3 operator-(f3 a, f3 b) { return mk3(a.x - b.x, a.y - b.y, a.z - b.z); }
+__device__ __forceinline__ f3 operator*(f3 a, float s) { return mk3(a.x * s, a.y * s, a.z * s); }
+__device__ __forceinline__ float dot(f3 a, f3 b) { return fmaf(a.x, b.x, fmaf(a.y, b.y, a.z * b.z)); }
+__device__ __forceinline__ f3 cross(f3 a, f3 b) { return mk3(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x); }
+__device__ __forceinline__ float norm3(f3 a) { return sqrtf(dot(a, a)); }
+__device__ __forceinline__ f3 ld3(const float* p) { return mk3(p[0], p[1], p[2]); }
+__device__ __forceinline__ void st3(float* p, f3 v) { p[0] = v.x; p[1] = v.y; p[2] = v.z; }
+__device__ __forceinline__ f3 unit3(f3 a) {
+  float n = norm3(a);
+  return n < MINVAL ? mk3(1.f, 0.f, 0.f) : a * (1.f / n);
+}
+__device__ __forceinline__ f3 mulM(const float* R, f3 v) {
+  return mk3(fmaf(R[0], v.x, fmaf(R[1], v.y, R[2] * v.z)), fmaf(R[3], v.x, fmaf(R[4], v.y, R[5] * v.z)),
+             fmaf(R[6], v.x, fmaf(R[7], v.y, R[8] * v.z)));
+}
+__device__ __forceinline__ f3 mulMT(const float* R, f3 v) {
+  return mk3(fmaf(R[0], v.x, fmaf(R[3], v.y, R[6] * v.z)), fmaf(R[1], v.x, fmaf(R[4], v.y, R[7] * v.z)),
+             fmaf(R[2], v.x, fmaf(R[5], v.y, R[8] * v.z)));
+}
+struct f4 { float w, x, y, z; };
+__device__ __forceinline__ f4 ld4(const float* p) { f4 q; q.w = p[0]; q.x = p[1]; q.y = p[2]; q.z = p[3]; return q; }
+__device__ __forceinline__ void st4(float* p, f4 q) { p[0] = q.w; p[1] = q.x; p[2] = q.y; p[3] = q.z; }
+__device__ __forceinline__ f4 qmul(f4 a, f4 b) {
+  f4 r;
+  r.w = a.w * b.w - a.x * b.x - a.y * b.y - a.z * b.z;
+  r.x = a.w * b.x + a.x * b.w + a.y * b.z - a.z * b.y;
+  r.y = a.w * b.y - a.x * b.z + a.y * b.w + a.z * b.x;
+  r.z = a.w * b.z + a.x * b.y - a.y * b.x + a.z * b.w;
+  return r;
+}
+__device__ __forceinline__ f4 qnormalize(f4 q) {
+  float n = sqrtf(q.w * q.w + q.x * q.x + q.y * q.y + q.z * q.z);
+  if (n < MINVAL) { q.w = 1.f; q.x = q.y = q.z = 0.f; return q; }
+  float s = 1.f / n;
+  q.w *= s; q.x *= s; q.y *= s; q.z *= s;
+  return q;
+}
+__device__ __forceinline__ void q2m(float* R, f4 q) {
+  float w = q.w, x = q.x, y = q.y, z = q.z;
+  R[0] = w * w + x * x - y * y - z * z; R[1] = 2.f * (x * y - w * z); R[2] = 2.f * (x * z + w * y);
+  R[3] = 2.f * (x * y + w * z); R[4] = w * w - x * x + y * y - z * z; R[5] = 2.f * (y * z - w * x);
+  R[6] = 2.f * (x * z - w * y); R[7] = 2.f * (y * z + w * x); R[8] = w * w - x * x - y * y + z * z;
+}
+__device__ __forceinline__ float clipf(float x, float lo, float hi) { return fminf(fmaxf(x, lo), hi); }
+__device__ __forceinline__ float warpSum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(FULLMASK, v, o);
+  return v;
+}
+// spatial algebra on [angular; linear] 6-vectors; inertia = (Ixx Iyy Izz Ixy Ixz Iyz, m*cx m*cy m*cz, m)
+__device__ __forceinline__ void inertMulVec(float* r, const float* I, const float* v) {
+  f3 w = ld3(v), l = ld3(v + 3), mc = ld3(I + 6);
+  f3 Iw = mk3(I[0] * w.x + I[3] * w.y + I[4] * w.z, I[3] * w.x + I[1] * w.y + I[5] * w.z, I[4] * w.x + I[5] * w.y + I[2] * w.z);
+  st3(r, Iw + cross(mc, l));
+  st3(r + 3, l * I[9] + cross(w, mc));
+}
+__device__ __forceinline__ void crossMotion(float* r, const float* vel, const float* v) {
+  f3 w = ld3(vel), l = ld3(vel + 3), a = ld3(v), b = ld3(v + 3);
+  st3(r, cross(w, a)); st3(r + 3, cross(w, b) + cross(l, a));
+}
+__device__ __forceinline__ void crossForce(float* r, const float* vel, const float* f) {
+  f3 w = ld3(vel), l = ld3(vel + 3), a = ld3(f), b = ld3(f + 3);
+  st3(r, cross(w, a) + cross(l, b)); st3(r + 3, cross(w, b));
+}
+
+// frame record in shared memory: pos[3], quat[4], mat[9]
+#define FR_POS(sm, L, f) ((sm) + (L).frames + 16 * (f))
+#define FR_QUAT(sm, L, f) ((sm) + (L).frames + 16 * (f) + 3)
+#define FR_MAT(sm, L, f) ((sm) + (L).frames + 16 * (f) + 7)
+
+// ------------------------------------------------------------------------------------------ kinematics
+__device__ void kinematics(const DevModel& D, const SmemLayout& L, float* sm, int lane) {
+  if (lane == 0) {
+    float* p = FR_POS(sm, L, 0);
+    p[0] = p[1] = p[2] = 0.f; p[3] = 1.f; p[4] = p[5] = p[6] = 0.f;
+    p[7] = 1.f; p[8] = 0.f; p[9] = 0.f; p[10] = 0.f; p[11] = 1.f; p[12] = 0.f; p[13] = 0.f; p[14] = 0.f; p[15] = 1.f;
+  }
+  __syncwarp();
+  float* qpos = sm + L.qpos;
+  for (int l = 0; l < D.nlevel; l++) {
+    for (int idx = D.lvl_start[l] + lane; idx < D.lvl_start[l + 1]; idx += 32) {
+      const int f = D.lvl_frames[idx], p = D.fr_parent[f], ja = D.fr_jntadr[f], jn = D.fr_jntnum[f];
+      f3 pos; f4 quat; float R[9];
+      if (jn == 1 && D.jnt_type[ja] == JNT_FREE) {
+        const int qa = D.jnt_qposadr[ja];
+        pos = ld3(qpos + qa);
+        quat = qnormalize(ld4(qpos + qa + 3));
+        st4(qpos + qa + 3, quat);
+        st3(sm + L.xanchor + 3 * ja, pos); st3(sm + L.xaxis + 3 * ja, ld3(D.jnt_axis + 3 * ja));
+      } else {
+        pos = ld3(FR_POS(sm, L, p)) + mulM(FR_MAT(sm, L, p), ld3(D.fr_pre_pos + 3 * f));
+        quat = qmul(ld4(FR_QUAT(sm, L, p)), ld4(D.fr_pre_quat + 4 * f));
+        q2m(R, quat);
+        for (int j = ja; j < ja + jn; j++) {
+          const f3 lpos = ld3(D.jnt_pos + 3 * j), laxis = ld3(D.jnt_axis + 3 * j);
+          const f3 anchor = mulM(R, lpos) + pos, axis = mulM(R, laxis);
+          st3(sm + L.xanchor + 3 * j, anchor); st3(sm + L.xaxis + 3 * j, axis);
+          const int qa = D.jnt_qposadr[j];
+          const float d = qpos[qa] - D.qpos0[qa];
+          if (D.jnt_type[j] == JNT_SLIDE) pos = pos + axis * d;
+          else {
+            float sn, cs; sincosf(0.5f * d, &sn, &cs);
+            f4 ql; ql.w = cs; ql.x = laxis.x * sn; ql.y = laxis.y * sn; ql.z = laxis.z * sn;
+            quat = qmul(quat, ql);
+            q2m(R, quat);
+            pos = anchor - mulM(R, lpos);
+          }
+        }
+      }
+      quat = qnormalize(quat);
+      q2m(R, quat);
+      float* o = FR_POS(sm, L, f);
+      st3(o, pos); st4(o + 3, quat);
+#pragma unroll
+      for (int k = 0; k < 9; k++) o[7 + k] = R[k];
+    }
+    __syncwarp();
+  }
+}
+
+// composite inertia of every frame about its tree's centre of mass, motion axes (mj_comPos over weld groups)
+__device__ void comPos(const DevModel& D, const SmemLayout& L, float* sm, int lane) {
+  float* cin = sm + L.cinert;
+  for (int f = lane; f < D.nframe; f += 32) {
+    f3 cw = ld3(FR_POS(sm, L, f)) + mulM(FR_MAT(sm, L, f), ld3(D.fr_com + 3 * f));
+    st3(cin + 10 * f + 6, cw); cin[10 * f + 9] = D.fr_mass[f];
+  }
+  __syncwarp();
+  for (int r = lane; r < D.nroot; r += 32) {
+    f3 acc = ld3(D.root_const + 4 * r);
+    const float M = D.root_const[4 * r + 3];
+    for (int f = D.root_fstart[r]; f < D.root_fend[r]; f++) acc = acc + ld3(cin + 10 * f + 6) * cin[10 * f + 9];
+    if (M < MINVAL) acc = mk3(0.f, 0.f, 0.f); else acc = acc * (1.f / M);
+    st3(sm + L.rootcom + 3 * r, acc);
+  }
+  __syncwarp();
+  for (int f = lane; f < D.nframe; f += 32) {
+    float* c = cin + 10 * f;
+    if (f == 0) { for (int k = 0; k < 10; k++) c[k] = 0.f; continue; }
+    const float* R = FR_MAT(sm, L, f);
+    const float* I = D.fr_inertia + 6 * f;
+    const float m = c[9];
+    const f3 off = ld3(c + 6) - ld3(sm + L.rootcom + 3 * D.fr_root[f]);
+    // T = R * Ilocal (Ilocal symmetric: xx yy zz xy xz yz), Iw = T * R^T
+    float T[9];
+#pragma unroll
+    for (int i = 0; i < 3; i++) {
+      T[3 * i] = R[3 * i] * I[0] + R[3 * i + 1] * I[3] + R[3 * i + 2] * I[4];
+      T[3 * i + 1] = R[3 * i] * I[3] + R[3 * i + 1] * I[1] + R[3 * i + 2] * I[5];
+      T[3 * i + 2] = R[3 * i] * I[4] + R[3 * i + 1] * I[5] + R[3 * i + 2] * I[2];
+    }
+    const float xx = T[0] * R[0] + T[1] * R[1] + T[2] * R[2], yy = T[3] * R[3] + T[4] * R[4] + T[5] * R[5],
+                zz = T[6] * R[6] + T[7] * R[7] + T[8] * R[8], xy = T[0] * R[3] + T[1] * R[4] + T[2] * R[5],
+                xz = T[0] * R[6] + T[1] * R[7] + T[2] * R[8], yz = T[3] * R[6] + T[4] * R[7] + T[5] * R[8];
+    c[0] = xx + m * (off.y * off.y + off.z * off.z); c[1] = yy + m * (off.x * off.x + off.z * off.z);
+    c[2] = zz + m * (off.x * off.x + off.y * off.y); c[3] = xy - m * off.x * off.y; c[4] = xz - m * off.x * off.z;
+    c[5] = yz - m * off.y * off.z; c[6] = m * off.x; c[7] = m * off.y; c[8] = m * off.z;
+  }
+  for (int j = lane; j < D.njnt; j += 32) {
+    const int f = D.jnt_frame[j], da = D.jnt_dofadr[j];
+    const f3 off = ld3(sm + L.rootcom + 3 * D.fr_root[f]) - ld3(sm + L.xanchor + 3 * j);
+    const f3 axis = ld3(sm + L.xaxis + 3 * j);
+    float* cd = sm + L.cdof + 6 * da;
+    const int ty = D.jnt_type[j];
+    if (ty == JNT_FREE) {
+      const float* R = FR_MAT(sm, L, f);
+#pragma unroll
+      for (int k = 0; k < 3; k++) {
+        st3(cd + 6 * k, mk3(0.f, 0.f, 0.f)); st3(cd + 6 * k + 3, mk3(k == 0, k == 1, k == 2));
+        const f3 ax = mk3(R[k], R[3 + k], R[6 + k]);
+        st3(cd + 6 * (3 + k), ax); st3(cd + 6 * (3 + k) + 3, cross(ax, off));
+      }
+    } else if (ty == JNT_SLIDE) {
+      st3(cd, mk3(0.f, 0.f, 0.f)); st3(cd + 3, axis);
+    } else {
+      st3(cd, axis); st3(cd + 3, cross(axis, off));
+    }
+  }
+  __syncwarp();
+}
+
+// ------------------------------------------------------------------------------------------ mjData position outputs
+// Written straight to global memory (world-major rows); nothing here feeds the dynamics.
+__device__ void writePositionOutputs(const DevModel& D, const SmemLayout& L, const FieldPtrs& F, float* sm, int lane, size_t w) {
+  float* xpos = (float*)F.p[MYO_F_XPOS]; float* xquat = (float*)F.p[MYO_F_XQUAT]; float* xmat = (float*)F.p[MYO_F_XMAT];
+  float* xipos = (float*)F.p[MYO_F_XIPOS]; float* ximat = (float*)F.p[MYO_F_XIMAT]; float* cinert = (float*)F.p[MYO_F_CINERT];
+  const int nb = D.nbody;
+  if (xpos || xquat || xmat || xipos || ximat || cinert) {
+    for (int b = lane; b < nb; b += 32) {
+      const int f = D.body_frame[b];
+      const float* R = FR_MAT(sm, L, f);
+      const f3 pos = ld3(FR_POS(sm, L, f)) + mulM(R, ld3(D.body_off_pos + 3 * b));
+      const f4 q = qnormalize(qmul(ld4(FR_QUAT(sm, L, f)), ld4(D.body_off_quat + 4 * b)));
+      float M[9]; q2m(M, q);
+      if (xpos) st3(xpos + (w * nb + b) * 3, pos);
+      if (xquat) st4(xquat + (w * nb + b) * 4, q);
+      if (xmat) for (int k = 0; k < 9; k++) xmat[(w * nb + b) * 9 + k] = M[k];
+      const f3 ip = pos + mulM(M, ld3(D.body_ipos + 3 * b));
+      if (xipos) st3(xipos + (w * nb + b) * 3, ip);
+      if (ximat || cinert) {
+        float IM[9]; q2m(IM, qmul(q, ld4(D.body_iquat + 4 * b)));
+        if (ximat) for (int k = 0; k < 9; k++) ximat[(w * nb + b) * 9 + k] = IM[k];
+        if (cinert) {
+          float* c = cinert + (w * nb + b) * 10;
+          if (b == 0) { for (int k = 0; k < 10; k++) c[k] = 0.f; }
+          else {
+            const float m = D.body_mass[b], i0 = D.body_inertia[3 * b], i1 = D.body_inertia[3 * b + 1], i2 = D.body_inertia[3 * b + 2];
+            const f3 off = ip - ld3(sm + L.rootcom + 3 * D.body_root[b]);
+            c[0] = IM[0] * IM[0] * i0 + IM[1] * IM[1] * i1 + IM[2] * IM[2] * i2 + m * (off.y * off.y + off.z * off.z);
+            c[1] = IM[3] * IM[3] * i0 + IM[4] * IM[4] * i1 + IM[5] * IM[5] * i2 + m * (off.x * off.x + off.z * off.z);
+            c[2] = IM[6] * IM[6] * i0 + IM[7] * IM[7] * i1 + IM[8] * IM[8] * i2 + m * (off.x * off.x + off.y * off.y);
+            c[3] = IM[0] * IM[3] * i0 + IM[1] * IM[4] * i1 + IM[2] * IM[5] * i2 - m * off.x * off.y;
+            c[4] = IM[0] * IM[6] * i0 + IM[1] * IM[7] * i1 + IM[2] * IM[8] * i2 - m * off.x * off.z;
+            c[5] = IM[3] * IM[6] * i0 + IM[4] * IM[7] * i1 + IM[5] * IM[8] * i2 - m * off.y * off.z;
+            c[6] = m * off.x; c[7] = m * off.y; c[8] = m * off.z; c[9] = m;
+          }
+        }
+      }
+    }
+  }
+  float* scom = (float*)F.p[MYO_F_SUBTREE_COM];
+  float* crb = (float*)F.p[MYO_F_CRB];
+  if ((scom && xipos) || (crb && cinert)) {
+    __syncwarp();  // the loops below read back what other lanes of this warp just wrote (L2 loads, ld.global.cg)
+    for (int b = lane; b < nb; b += 32) {
+      const int e = D.body_subend[b];
+      if (scom && xipos) {
+        f3 acc = mk3(0.f, 0.f, 0.f);
+        for (int c = b; c < e; c++) {
+          const float* xp = xipos + (w * nb + c) * 3;
+          acc = acc + mk3(__ldcg(xp), __ldcg(xp + 1), __ldcg(xp + 2)) * D.body_mass[c];
+        }
+        const float M = D.body_subtreemass[b];
+        const float* xb = xipos + (w * nb + b) * 3;
+        if (M < MINVAL) acc = mk3(__ldcg(xb), __ldcg(xb + 1), __ldcg(xb + 2)); else acc = acc * (1.f / M);
+        st3(scom + (w * nb + b) * 3, acc);
+      }
+      if (crb && cinert) {
+        float acc[10];
+        for (int k = 0; k < 10; k++) acc[k] = 0.f;
+        if (b > 0) for (int c = b; c < e; c++) for (int k = 0; k < 10; k++) acc[k] += __ldcg(cinert + (w * nb + c) * 10 + k);
+        for (int k = 0; k < 10; k++) crb[(w * nb + b) * 10 + k] = acc[k];
+      }
+    }
+  }
+  float* xa = (float*)F.p[MYO_F_XANCHOR]; float* xx = (float*)F.p[MYO_F_XAXIS];
+  if (xa) for (int i = lane; i < 3 * D.njnt; i += 32) xa[w * 3 * D.njnt + i] = sm[L.xanchor + i];
+  if (xx) for (int i = lane; i < 3 * D.njnt; i += 32) xx[w * 3 * D.njnt + i] = sm[L.xaxis + i];
+  float* cd = (float*)F.p[MYO_F_CDOF];
+  if (cd) for (int i = lane; i < 6 * D.nv; i += 32) cd[w * 6 * D.nv + i] = sm[L.cdof + i];
+  float* gp = (float*)F.p[MYO_F_GEOM_XPOS]; float* gm = (float*)F.p[MYO_F_GEOM_XMAT];
+  if (gp || gm) {
+    const int ng = D.ngeom;
+    for (int g = lane; g < ng; g += 32) {
+      const int f = D.geom_frame[g];
+      if (gp) st3(gp + (w * ng + g) * 3, ld3(FR_POS(sm, L, f)) + mulM(FR_MAT(sm, L, f), ld3(D.geom_lpos + 3 * g)));
+      if (gm) {
+        float M[9]; q2m(M, qnormalize(qmul(ld4(FR_QUAT(sm, L, f)), ld4(D.geom_lquat + 4 * g))));
+        for (int k = 0; k < 9; k++) gm[(w * ng + g) * 9 + k] = M[k];
+      }
+    }
+  }
+  float* sp = (float*)F.p[MYO_F_SITE_XPOS]; float* smt = (float*)F.p[MYO_F_SITE_XMAT];
+  if (sp || smt) {
+    const int ns = D.nsite;
+    for (int s = lane; s < ns; s += 32) {
+      const int f = D.site_frame[s];
+      if (sp) st3(sp + (w * ns + s) * 3, ld3(FR_POS(sm, L, f)) + mulM(FR_MAT(sm, L, f), ld3(D.site_lpos + 3 * s)));
+      if (smt) {
+        float M[9]; q2m(M, qnormalize(qmul(ld4(FR_QUAT(sm, L, f)), ld4(D.site_lquat + 4 * s))));
+        for (int k = 0; k < 9; k++) smt[(w * ns + s) * 9 + k] = M[k];
+      }
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------ tendon wrapping (mju_wrap)
+__device__ __forceinline__ bool segIntersect(const float* p1, const float* p2, const float* p3, const float* p4) {
+  const float det = (p4[1] - p3[1]) * (p2[0] - p1[0]) - (p4[0] - p3[0]) * (p2[1] - p1[1]);
+  if (fabsf(det) < MINVAL) return false;
+  const float a = ((p4[0] - p3[0]) * (p1[1] - p3[1]) - (p4[1] - p3[1]) * (p1[0] - p3[0])) / det;
+  const float b = ((p2[0] - p1[0]) * (p1[1] - p3[1]) - (p2[1] - p1[1]) * (p1[0] - p3[0])) / det;
+  return a >= 0.f && a <= 1.f && b >= 0.f && b <= 1.f;
+}
+__device__ float wrapCircle(float* pnt, const float* d, const float* sd, float rad) {
+  const float sq0 = d[0] * d[0] + d[1] * d[1], sq1 = d[2] * d[2] + d[3] * d[3], sqr = rad * rad;
+  const float dx = d[2] - d[0], dy = d[3] - d[1];
+  const float dd = dx * dx + dy * dy;
+  float a = -(dx * d[0] + dy * d[1]) / fmaxf(MINVAL, dd);
+  a = clipf(a, 0.f, 1.f);
+  const float nx = d[0] + a * dx, ny = d[1] + a * dy;
+  if (nx * nx + ny * ny > sqr && (!sd || sd[0] * nx + sd[1] * ny >= 0.f)) return -1.f;
+  if (sq0 < sqr || sq1 < sqr) return -1.f;
+  const float s0 = sqrtf(sq0 - sqr), s1 = sqrtf(sq1 - sqr);
+  float sol[2][4], good[2];
+#pragma unroll
+  for (int i = 0; i < 2; i++) {
+    const float sg = i == 0 ? 1.f : -1.f;
+    sol[i][0] = (d[0] * sqr + sg * rad * d[1] * s0) / sq0;
+    sol[i][1] = (d[1] * sqr - sg * rad * d[0] * s0) / sq0;
+    sol[i][2] = (d[2] * sqr - sg * rad * d[3] * s1) / sq1;
+    sol[i][3] = (d[3] * sqr + sg * rad * d[2] * s1) / sq1;
+    if (sd) {
+      const float tx = sol[i][0] + sol[i][2], ty = sol[i][1] + sol[i][3];
+      good[i] = (tx * sd[0] + ty * sd[1]) / fmaxf(MINVAL, sqrtf(tx * tx + ty * ty));
+    } else {
+      const float tx = sol[i][0] - sol[i][2], ty = sol[i][1] - sol[i][3];
+      good[i] = -(tx * tx + ty * ty);
+    }
+    if (segIntersect(d, sol[i], d + 2, sol[i] + 2)) good[i] = -10000.f;
+  }
+  const int i = good[0] > good[1] ? 0 : 1;
+#pragma unroll
+  for (int k = 0; k < 4; k++) pnt[k] = i == 0 ? sol[0][k] : sol[1][k];
+  if (segIntersect(d, pnt, d + 2, pnt + 2)) return -1.f;
+  const float n0 = fmaxf(MINVAL, sqrtf(pnt[0] * pnt[0] + pnt[1] * pnt[1])), n1 = fmaxf(MINVAL, sqrtf(pnt[2] * pnt[2] + pnt[3] * pnt[3]));
+  float ang = acosf(clipf((pnt[0] * pnt[2] + pnt[1] * pnt[3]) / (n0 * n1), -1.f, 1.f));
+  const float cr = pnt[1] * pnt[2] - pnt[0] * pnt[3];
+  if ((cr > 0.f && i) || (cr < 0.f && !i)) ang = 2.f * CUDART_PI_F - ang;
+  return rad * ang;
+}
+__device__ float wrapInside(float* pnt, const float* d, float rad) {
+  const float l0 = sqrtf(d[0] * d[0] + d[1] * d[1]), l1 = sqrtf(d[2] * d[2] + d[3] * d[3]);
+  if (l0 <= rad || l1 <= rad) return -1.f;
+  const float dx = d[2] - d[0], dy = d[3] - d[1];
+  const float dd = dx * dx + dy * dy;
+  if (dd > MINVAL) {
+    const float a = -(dx * d[0] + dy * d[1]) / dd;
+    if (a > 0.f && a < 1.f) {
+      const float tx = d[0] + a * dx, ty = d[1] + a * dy;
+      if (sqrtf(tx * tx + ty * ty) <= rad) return -1.f;
+    }
+  }
+  const float mx = 0.5f * (d[0] + d[2]), my = 0.5f * (d[1] + d[3]);
+  const float mn = fmaxf(MINVAL, sqrtf(mx * mx + my * my));
+  pnt[0] = pnt[2] = rad * mx / mn; pnt[1] = pnt[3] = rad * my / mn;
+  const float A = rad / l0, B = rad / l1;
+  const float cosG = (l0 * l0 + l1 * l1 - dd) / (2.f * l0 * l1);
+  if (cosG < -1.f + 1e-7f) return -1.f;
+  if (cosG > 1.f - 1e-7f) return 0.f;
+  const float G = acosf(cosG);
+  float z = 1.f - 1e-6f;
+  float f = asinf(A * z) + asinf(B * z) - 2.f * asinf(z) + G;
+  if (f > 0.f) return 0.f;
+  int it = 0;
+  for (; it < 20 && fabsf(f) > 1e-6f; it++) {
+    const float df = A / fmaxf(MINVAL, sqrtf(1.f - z * z * A * A)) + B / fmaxf(MINVAL, sqrtf(1.f - z * z * B * B)) -
+                     2.f / fmaxf(MINVAL, sqrtf(1.f - z * z));
+    if (df > -MINVAL) return 0.f;
+    const float z1 = z - f / df;
+    if (z1 > z) return 0.f;
+    z = z1;
+    f = asinf(A * z) + asinf(B * z) - 2.f * asinf(z) + G;
+    if (f > 1e-6f) return 0.f;
+  }
+  if (it >= 20) return 0.f;
+  float vx, vy, ang;
+  if (d[0] * d[3] - d[1] * d[2] > 0.f) { vx = d[0] / l0; vy = d[1] / l0; ang = asinf(z) - asinf(A * z); }
+  else { vx = d[2] / l1; vy = d[3] / l1; ang = asinf(z) - asinf(B * z); }
+  float sn, cs; sincosf(ang, &sn, &cs);
+  pnt[0] = pnt[2] = rad * (cs * vx - sn * vy);
+  pnt[1] = pnt[3] = rad * (sn * vx + cs * vy);
+  return 0.f;
+}
+// returns wrap length or -1; w0/w1 = world tangent points
+__device__ float wrapGeom(f3 x0, f3 x1, f3 gpos, const float* gmat, float radius, int type, bool hasSide, f3 side, f3* w0, f3* w1) {
+  if (radius < MINVAL) return -1.f;
+  const f3 p0 = mulMT(gmat, x0 - gpos), p1 = mulMT(gmat, x1 - gpos);
+  if (norm3(p0) < MINVAL || norm3(p1) < MINVAL) return -1.f;
+  f3 ax0, ax1;
+  if (type == UNIT_SPHERE) {
+    ax0 = unit3(p0);
+    f3 nrm = cross(p0, p1);
+    const float n = norm3(nrm);
+    if (n < MINVAL) {
+      const float a0 = fabsf(ax0.x), a1 = fabsf(ax0.y), a2 = fabsf(ax0.z);
+      const int k = (a0 >= a1 && a0 >= a2) ? 0 : (a1 >= a2 ? 1 : 2);
+      nrm = unit3(cross(ax0, mk3(k != 0, k != 1, k != 2)));
+    } else nrm = nrm * (1.f / n);
+    ax1 = unit3(cross(nrm, ax0));
+  } else { ax0 = mk3(1.f, 0.f, 0.f); ax1 = mk3(0.f, 1.f, 0.f); }
+  float d[4] = {dot(p0, ax0), dot(p0, ax1), dot(p1, ax0), dot(p1, ax1)};
+  float sd[2] = {0.f, 0.f};
+  bool inside = false;
+  if (hasSide) {
+    const f3 s = mulMT(gmat, side - gpos);
+    sd[0] = dot(s, ax0); sd[1] = dot(s, ax1);
+    const float n = radius / fmaxf(MINVAL, sqrtf(sd[0] * sd[0] + sd[1] * sd[1]));
+    sd[0] *= n; sd[1] *= n;
+    inside = norm3(s) < radius;
+  }
+  float pnt[4];
+  float wlen = inside ? wrapInside(pnt, d, radius) : wrapCircle(pnt, d, hasSide ? sd : nullptr, radius);
+  if (wlen < 0.f) return -1.f;
+  f3 r0 = ax0 * pnt[0] + ax1 * pnt[1], r1 = ax0 * pnt[2] + ax1 * pnt[3];
+  if (type == UNIT_CYLINDER) {
+    const float L0 = sqrtf((p0.x - r0.x) * (p0.x - r0.x) + (p0.y - r0.y) * (p0.y - r0.y));
+    const float L1 = sqrtf((p1.x - r1.x) * (p1.x - r1.x) + (p1.y - r1.y) * (p1.y - r1.y));
+    const float tot = fmaxf(MINVAL, L0 + wlen + L1);
+    r0.z = p0.z + (p1.z - p0.z) * L0 / tot;
+    r1.z = p0.z + (p1.z - p0.z) * (L0 + wlen) / tot;
+    const float h = r1.z - r0.z;
+    wlen = sqrtf(wlen * wlen + h * h);
+  }
+  *w0 = mulM(gmat, r0) + gpos; *w1 = mulM(gmat, r1) + gpos;
+  return wlen;
+}
+
+// mj_tendon: path lengths + sparse moment arms
+__device__ void tendons(const DevModel& D, const SmemLayout& L, const FieldPtrs& F, float* sm, int lane, size_t w) {
+  for (int u = lane; u < D.nunit; u += 32) {
+    const int s0 = D.unit_s0[u], s1 = D.unit_s1[u], g = D.unit_geom[u];
+    const int f0 = D.site_frame[s0], f1 = D.site_frame[s1];
+    const f3 p0 = ld3(FR_POS(sm, L, f0)) + mulM(FR_MAT(sm, L, f0), ld3(D.site_lpos + 3 * s0));
+    const f3 p1 = ld3(FR_POS(sm, L, f1)) + mulM(FR_MAT(sm, L, f1), ld3(D.site_lpos + 3 * s1));
+    float wlen = -1.f; f3 w0 = p0, w1 = p1;
+    if (g >= 0) {
+      const int fg = D.geom_frame[g], sid = D.unit_side[u];
+      const f3 gpos = ld3(FR_POS(sm, L, fg)) + mulM(FR_MAT(sm, L, fg), ld3(D.geom_lpos + 3 * g));
+      float gm[9]; q2m(gm, qnormalize(qmul(ld4(FR_QUAT(sm, L, fg)), ld4(D.geom_lquat + 4 * g))));
+      f3 side = mk3(0.f, 0.f, 0.f);
+      if (sid >= 0) { const int fs = D.site_frame[sid]; side = ld3(FR_POS(sm, L, fs)) + mulM(FR_MAT(sm, L, fs), ld3(D.site_lpos + 3 * sid)); }
+      wlen = wrapGeom(p0, p1, gpos, gm, D.unit_radius[u], D.unit_type[u], sid >= 0, side, &w0, &w1);
+    }
+    const int sl0 = D.unit_slot[2 * u], sl1 = D.unit_slot[2 * u + 1];
+    float len;
+    if (wlen < 0.f) {
+      const f3 dif = p1 - p0; const float n = norm3(dif);
+      len = n;
+      if (sl0 >= 0) { st3(sm + L.slots + 6 * sl0, p0); st3(sm + L.slots + 6 * sl0 + 3, n > MINVAL ? dif * (1.f / n) : mk3(0.f, 0.f, 0.f)); }
+    } else {
+      const f3 d0 = w0 - p0, d1 = p1 - w1; const float n0 = norm3(d0), n1 = norm3(d1);
+      len = n0 + wlen + n1;
+      if (sl0 >= 0) { st3(sm + L.slots + 6 * sl0, p0); st3(sm + L.slots + 6 * sl0 + 3, n0 > MINVAL ? d0 * (1.f / n0) : mk3(0.f, 0.f, 0.f)); }
+      if (sl1 >= 0) { st3(sm + L.slots + 6 * sl1, w1); st3(sm + L.slots + 6 * sl1 + 3, n1 > MINVAL ? d1 * (1.f / n1) : mk3(0.f, 0.f, 0.f)); }
+    }
+    sm[L.ulen + u] = len / D.unit_div[u];
+    sm[L.uwrap + u] = wlen < 0.f ? 0.f : 1.f;
+  }
+  __syncwarp();
+  for (int n = lane; n < D.nnz; n += 32) {
+    float acc = 0.f;
+    for (int e = D.nz_estart[n]; e < D.nz_estart[n + 1]; e++) {
+      const int kind = D.ent_kind[e];
+      if (kind != ENT_ALWAYS) {
+        const bool wrapped = sm[L.uwrap + D.ent_unit[e]] != 0.f;
+        if ((kind == ENT_WRAP) != wrapped) continue;
+      }
+      const int i = D.ent_dof[e], sl = D.ent_slot[e];
+      const f3 p = ld3(sm + L.slots + 6 * sl), dir = ld3(sm + L.slots + 6 * sl + 3);
+      const f3 com = ld3(sm + L.rootcom + 3 * D.fr_root[D.dof_frame[i]]);
+      const float* cd = sm + L.cdof + 6 * i;
+      acc += D.ent_scale[e] * (dot(ld3(cd), cross(p - com, dir)) + dot(ld3(cd + 3), dir));
+    }
+    sm[L.tenJ + n] = acc;
+  }
+  for (int t = lane; t < D.nten; t += 32) {
+    float acc = 0.f;
+    for (int u = D.ten_ustart[t]; u < D.ten_ustart[t + 1]; u++) acc += sm[L.ulen + u];
+    sm[L.tenlen + t] = acc;
+  }
+  __syncwarp();
+  float* tl = (float*)F.p[MYO_F_TEN_LENGTH]; float* tj = (float*)F.p[MYO_F_TEN_J];
+  if (tl) for (int t = lane; t < D.nten; t += 32) tl[w * D.nten + t] = sm[L.tenlen + t];
+  if (tj) {
+    const size_t n = (size_t)D.nten * D.nv;
+    for (int i = lane; i < (int)n; i += 32) tj[w * n + i] = 0.f;
+    __syncwarp();
+    for (int k = lane; k < D.nnz; k += 32) tj[w * n + (size_t)D.nz_tendon[k] * D.nv + D.nz_dof[k]] = sm[L.tenJ + k];
+  }
+}
+
+// ------------------------------------------------------------------------------------------ inertia: mj_crb, mj_factorM, mj_solveM
+// sparse L^T D L in place over the dof-tree pattern; one precomputed multiply-subtract list per column
+__device__ void factorLDL(const DevModel& D, float* LD, float* dinv, int lane) {
+  const int nv = D.nv;
+  for (int pos = 0; pos < nv; pos++) {
+    const int k = nv - 1 - pos, akk = D.dof_Madr[k];
+    const float inv = 1.f / LD[akk];
+    for (int o = D.ldl_start[pos] + lane; o < D.ldl_start[pos + 1]; o += 32) LD[D.ldl_dst[o]] -= LD[D.ldl_a[o]] * LD[D.ldl_b[o]] * inv;
+    __syncwarp();
+    const int d = D.dof_rowlen[k];
+    for (int s = 1 + lane; s < d; s += 32) LD[akk + s] *= inv;
+    if (lane == 0) dinv[k] = inv;
+    __syncwarp();
+  }
+}
+// x <- (L^T D L)^-1 x, by dof-tree levels
+__device__ void solveLDL(const DevModel& D, const float* LD, const float* dinv, float* x, int lane) {
+  for (int l = D.ndlevel - 1; l >= 0; l--) {
+    for (int idx = D.dlvl_start[l] + lane; idx < D.dlvl_start[l + 1]; idx += 32) {
+      const int j = D.dlvl_dofs[idx];
+      float acc = x[j];
+      for (int e = D.desc_start[j]; e < D.desc_start[j + 1]; e++) acc -= LD[D.desc_idx[e]] * x[D.desc_dof[e]];
+      x[j] = acc;
+    }
+    __syncwarp();
+  }
+  for (int i = lane; i < D.nv; i += 32) x[i] *= dinv[i];
+  __syncwarp();
+  for (int l = 1; l < D.ndlevel; l++) {
+    for (int idx = D.dlvl_start[l] + lane; idx < D.dlvl_start[l + 1]; idx += 32) {
+      const int i = D.dlvl_dofs[idx], a = D.dof_Madr[i], d = D.dof_rowlen[i];
+      float acc = x[i];
+      for (int s = 1; s < d; s++) acc -= LD[a + s] * x[D.M_col[a + s]];
+      x[i] = acc;
+    }
+    __syncwarp();
+  }
+}
+__device__ void inertia(const DevModel& D, const SmemLayout& L, const FieldPtrs& F, float* sm, int lane, size_t w) {
+  const int nv = D.nv;
+  // composite inertia of each frame's subtree (frames are in DFS order: subtree = contiguous range)
+  for (int i = lane; i < 10 * D.nframe; i += 32) {
+    const int f = i / 10, k = i - 10 * f;
+    float acc = 0.f;
+    if (f > 0) for (int g = f; g < D.fr_subend[f]; g++) acc += sm[L.cinert + 10 * g + k];
+    sm[L.crb + i] = acc;
+  }
+  __syncwarp();
+  float* f6 = sm + L.cdof_dot;  // scratch until the velocity stage
+  for (int i = lane; i < nv; i += 32) inertMulVec(f6 + 6 * i, sm + L.crb + 10 * D.dof_frame[i], sm + L.cdof + 6 * i);
+  __syncwarp();
+  for (int e = lane; e < D.nM; e += 32) {
+    const int r = D.M_row[e], c = D.M_col[e];
+    const float* a = sm + L.cdof + 6 * c; const float* b = f6 + 6 * r;
+    float s = a[0] * b[0] + a[1] * b[1] + a[2] * b[2] + a[3] * b[3] + a[4] * b[4] + a[5] * b[5];
+    if (r == c) s += D.dof_armature[r];
+    sm[L.qM + e] = s; sm[L.qLD + e] = s;
+  }
+  __syncwarp();
+  factorLDL(D, sm + L.qLD, sm + L.qLDinv, lane);
+  float* qMo = (float*)F.p[MYO_F_QM]; float* qLDo = (float*)F.p[MYO_F_QLD]; float* qdi = (float*)F.p[MYO_F_QLDIAGINV];
+  if (qMo || qLDo) {
+    const size_t n = (size_t)nv * nv;
+    for (int i = lane; i < (int)n; i += 32) { if (qMo) qMo[w * n + i] = 0.f; if (qLDo) qLDo[w * n + i] = 0.f; }
+    __syncwarp();
+    for (int e = lane; e < D.nM; e += 32) {
+      const int r = D.M_row[e], c = D.M_col[e];
+      if (qMo) { qMo[w * n + r * nv + c] = sm[L.qM + e]; qMo[w * n + c * nv + r] = sm[L.qM + e]; }
+      if (qLDo) qLDo[w * n + r * nv + c] = sm[L.qLD + e];
+    }
+  }
+  if (qdi) for (int i = lane; i < nv; i += 32) qdi[w * nv + i] = sm[L.qLDinv + i];
+}
+
+// ------------------------------------------------------------------------------------------ mj_fwdVelocity
+__device__ void velocity(const DevModel& D, const SmemLayout& L, const FieldPtrs& F, float* sm, int lane, size_t w) {
+  const int nv = D.nv;
+  const float* qvel = sm + L.qvel;
+  for (int t = lane; t < D.nten; t += 32) {
+    float acc = 0.f;
+    for (int n = D.ten_nzstart[t]; n < D.ten_nzstart[t + 1]; n++) acc += sm[L.tenJ + n] * qvel[D.nz_dof[n]];
+    sm[L.tenvel + t] = acc;
+  }
+  // body velocities: sum of the ancestor dof motions (all expressed about the tree's centre of mass)
+  for (int f = lane; f < D.nframe; f += 32) {
+    float v[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    if (f > 0) {
+      const int last = D.fr_dofadr[f] + D.fr_dofnum[f] - 1, a = D.dof_Madr[last], d = D.dof_rowlen[last];
+      for (int s = d - 1; s >= 0; s--) {
+        const int j = D.M_col[a + s]; const float qv = qvel[j]; const float* cd = sm + L.cdof + 6 * j;
+#pragma unroll
+        for (int k = 0; k < 6; k++) v[k] = fmaf(cd[k], qv, v[k]);
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < 6; k++) sm[L.cvel + 6 * f + k] = v[k];
+  }
+  for (int i = lane; i < nv; i += 32) {
+    const int pc = D.dof_prevcount[i], a = D.dof_Madr[i], d = D.dof_rowlen[i];
+    float* out = sm + L.cdof_dot + 6 * i;
+    if (pc < 0) { for (int k = 0; k < 6; k++) out[k] = 0.f; continue; }
+    float v[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (int s = d - 1; s >= pc; s--) {
+      const int j = D.M_col[a + s]; const float qv = qvel[j]; const float* cd = sm + L.cdof + 6 * j;
+#pragma unroll
+      for (int k = 0; k < 6; k++) v[k] = fmaf(cd[k], qv, v[k]);
+    }
+    crossMotion(out, v, sm + L.cdof + 6 * i);
+  }
+  __syncwarp();
+  const bool grav = !(D.disableflags & DSBL_GRAVITY);
+  for (int f = lane; f < D.nframe; f += 32) {
+    if (f == 0) { for (int k = 0; k < 6; k++) sm[L.cacc + k] = 0.f; continue; }
+    float a6[6] = {0.f, 0.f, 0.f, grav ? -D.gravity[0] : 0.f, grav ? -D.gravity[1] : 0.f, grav ? -D.gravity[2] : 0.f};
+    const int last = D.fr_dofadr[f] + D.fr_dofnum[f] - 1, a = D.dof_Madr[last], d = D.dof_rowlen[last];
+    for (int s = d - 1; s >= 0; s--) {
+      const int j = D.M_col[a + s]; const float qv = qvel[j]; const float* cd = sm + L.cdof_dot + 6 * j;
+#pragma unroll
+      for (int k = 0; k < 6; k++) a6[k] = fmaf(cd[k], qv, a6[k]);
+    }
+    float Ia[6], Iv[6], cf[6];
+    inertMulVec(Ia, sm + L.cinert + 10 * f, a6);
+    inertMulVec(Iv, sm + L.cinert + 10 * f, sm + L.cvel + 6 * f);
+    crossForce(cf, sm + L.cvel + 6 * f, Iv);
+#pragma unroll
+    for (int k = 0; k < 6; k++) sm[L.cacc + 6 * f + k] = Ia[k] + cf[k];   // cacc now holds the body force cfrc
+  }
+  __syncwarp();
+  const bool passive_on = !(D.disableflags & DSBL_PASSIVE);
+  for (int i = lane; i < nv; i += 32) {
+    const int f = D.dof_frame[i];
+    float acc[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (int g = f; g < D.fr_subend[f]; g++)
+#pragma unroll
+      for (int k = 0; k < 6; k++) acc[k] += sm[L.cacc + 6 * g + k];
+    const float* cd = sm + L.cdof + 6 * i;
+    sm[L.bias + i] = cd[0] * acc[0] + cd[1] * acc[1] + cd[2] * acc[2] + cd[3] * acc[3] + cd[4] * acc[4] + cd[5] * acc[5];
+    float spring = 0.f, damper = 0.f;
+    if (passive_on) {
+      const int j = D.dof_jnt[i];
+      const float k = D.jnt_stiffness[j];
+      if (k != 0.f && D.jnt_type[j] >= JNT_SLIDE) spring = -k * (sm[L.qpos + D.jnt_qposadr[j]] - D.qpos_spring[D.jnt_qposadr[j]]);
+      damper = -D.dof_damping[i] * qvel[i];
+      if (D.any_tendon_passive)
+        for (int c = D.col_start[i]; c < D.col_start[i + 1]; c++) {
+          const int n = D.col_nz[c], t = D.nz_tendon[n];
+          const float ks = D.ten_stiffness[t], kd = D.ten_damping[t], len = sm[L.tenlen + t];
+          if (ks > 0.f) {
+            const float lo = D.ten_lengthspring[2 * t], hi = D.ten_lengthspring[2 * t + 1];
+            const float fs = len > hi ? ks * (hi - len) : (len < lo ? ks * (lo - len) : 0.f);
+            spring += sm[L.tenJ + n] * fs;
+          }
+          if (kd > 0.f) damper -= kd * sm[L.tenvel + t] * sm[L.tenJ + n];
+        }
+    }
+    sm[L.passive + i] = spring + damper;
+    float* o;
+    if ((o = (float*)F.p[MYO_F_QFRC_SPRING])) o[w * nv + i] = spring;
+    if ((o = (float*)F.p[MYO_F_QFRC_DAMPER])) o[w * nv + i] = damper;
+    if ((o = (float*)F.p[MYO_F_QFRC_PASSIVE])) o[w * nv + i] = spring + damper;
+    if ((o = (float*)F.p[MYO_F_QFRC_BIAS])) o[w * nv + i] = sm[L.bias + i];
+  }
+  float* o;
+  if ((o = (float*)F.p[MYO_F_TEN_VELOCITY])) for (int t = lane; t < D.nten; t += 32) o[w * D.nten + t] = sm[L.tenvel + t];
+  if ((o = (float*)F.p[MYO_F_CDOF_DOT])) for (int i = lane; i < 6 * nv; i += 32) o[w * 6 * nv + i] = sm[L.cdof_dot + i];
+  if ((o = (float*)F.p[MYO_F_CVEL])) for (int i = lane; i < 6 * D.nbody; i += 32) o[w * 6 * D.nbody + i] = sm[L.cvel + 6 * D.body_frame[i / 6] + i % 6];
+  __syncwarp();
+}
+
+// ------------------------------------------------------------------------------------------ mj_fwdActuation
+__device__ __forceinline__ float muscleFL(float Ln, float lmin, float lmax) {
+  if (Ln < lmin || Ln > lmax) return 0.f;
+  const float a = 0.5f * (lmin + 1.f), b = 0.5f * (1.f + lmax);
+  float x;
+  if (Ln <= a) { x = (Ln - lmin) / fmaxf(MINVAL, a - lmin); return 0.5f * x * x; }
+  if (Ln <= 1.f) { x = (1.f - Ln) / fmaxf(MINVAL, 1.f - a); return 1.f - 0.5f * x * x; }
+  if (Ln <= b) { x = (Ln - 1.f) / fmaxf(MINVAL, b - 1.f); return 1.f - 0.5f * x * x; }
+  x = (lmax - Ln) / fmaxf(MINVAL, lmax - b);
+  return 0.5f * x * x;
+}
+__device__ void muscleGainBias(float len, float vel, const float* lr, float acc0, const float* prm, float* gain, float* bias) {
+  const float r0 = prm[0], r1 = prm[1], scale = prm[3], lmin = prm[4], lmax = prm[5], vmax = prm[6], fpmax = prm[7], fvmax = prm[8];
+  float force = prm[2];
+  if (force < 0.f) force = scale / fmaxf(MINVAL, acc0);
+  const float L0 = (lr[1] - lr[0]) / fmaxf(MINVAL, r1 - r0);
+  const float Ln = r0 + (len - lr[0]) / fmaxf(MINVAL, L0);
+  const float V = vel / fmaxf(MINVAL, L0 * vmax);
+  const float FL = muscleFL(Ln, lmin, lmax);
+  const float y = fvmax - 1.f;
+  float FV;
+  if (V <= -1.f) FV = 0.f;
+  else if (V <= 0.f) FV = (V + 1.f) * (V + 1.f);
+  else if (V <= y) FV = fvmax - (y - V) * (y - V) / fmaxf(MINVAL, y);
+  else FV = fvmax;
+  *gain = -force * FL * FV;
+  const float b = 0.5f * (1.f + lmax);
+  if (Ln <= 1.f) *bias = 0.f;
+  else if (Ln <= b) { const float x = (Ln - 1.f) / fmaxf(MINVAL, b - 1.f); *bias = -force * fpmax * 0.5f * x * x; }
+  else { const float x = (Ln - b) / fmaxf(MINVAL, b - 1.f); *bias = -force * fpmax * (0.5f + x); }
+}
+__device__ void actuation(const DevModel& D, const SmemLayout& L, const FieldPtrs& F, float* sm, int lane, size_t w) {
+  const int nu = D.nu, nv = D.nv;
+  const bool on = !(D.disableflags & DSBL_ACTUATION);
+  for (int i = lane; i < nu; i += 32) {
+    const int id = D.act_trnid[i];
+    const float gear = D.act_gear[i];
+    float len, vel;
+    if (D.act_trntype[i] == 3) { len = gear * sm[L.tenlen + id]; vel = gear * sm[L.tenvel + id]; }
+    else { len = gear * sm[L.qpos + D.jnt_qposadr[id]]; vel = gear * sm[L.qvel + D.jnt_dofadr[id]]; }
+    sm[L.actlen + i] = len; sm[L.actvel + i] = vel;
+    float force = 0.f, adot = 0.f;
+    const int aa = D.act_actadr[i];
+    if (on) {
+      float c = sm[L.ctrl + i];
+      const int fl = D.act_flags[i];
+      if ((fl & ACT_CTRLLIMITED) && !(D.disableflags & DSBL_CLAMPCTRL)) c = clipf(c, D.act_ctrlrange[2 * i], D.act_ctrlrange[2 * i + 1]);
+      float a = c;
+      if (aa >= 0) {
+        a = sm[L.act + aa];
+        const float* dp = D.act_dynprm + 3 * i;
+        const int dt = D.act_dyntype[i];
+        if (dt == DYN_INTEGRATOR) adot = c;
+        else if (dt == DYN_FILTER || dt == DYN_FILTEREXACT) adot = (c - a) / fmaxf(MINVAL, dp[0]);
+        else if (dt == DYN_MUSCLE) {
+          const float cc = clipf(c, 0.f, 1.f), ac = clipf(a, 0.f, 1.f);
+          const float ta = dp[0] * (0.5f + 1.5f * ac), td = dp[1] / (0.5f + 1.5f * ac), dctrl = cc - a;
+          float tau;
+          if (dp[2] < MINVAL) tau = dctrl > 0.f ? ta : td;
+          else { const float x = clipf(dctrl / dp[2] + 0.5f, 0.f, 1.f); tau = td + (ta - td) * (x * x * x * (x * (6.f * x - 15.f) + 10.f)); }
+          adot = dctrl / fmaxf(MINVAL, tau);
+        }
+      }
+      const float* gp = D.act_gainprm + 9 * i; const float* bp = D.act_biasprm + 9 * i;
+      float gain = 0.f, bias = 0.f, tmp;
+      const int gt = D.act_gaintype[i], bt = D.act_biastype[i];
+      if (gt == GAIN_FIXED) gain = gp[0];
+      else if (gt == GAIN_AFFINE) gain = gp[0] + gp[1] * len + gp[2] * vel;
+      else muscleGainBias(len, vel, D.act_lengthrange + 2 * i, D.act_acc0[i], gp, &gain, &tmp);
+      if (bt == BIAS_AFFINE) bias = bp[0] + bp[1] * len + bp[2] * vel;
+      else if (bt == BIAS_MUSCLE) muscleGainBias(len, vel, D.act_lengthrange + 2 * i, D.act_acc0[i], bp, &tmp, &bias);
+      force = gain * a + bias;
+      if (fl & ACT_FORCELIMITED) force = clipf(force, D.act_forcerange[2 * i], D.act_forcerange[2 * i + 1]);
+    }
+    sm[L.actforce + i] = force;
+    if (aa >= 0) sm[L.actdot + aa] = adot;
+  }
+  __syncwarp();
+  for (int t = lane; t < D.nten; t += 32) {
+    float acc = 0.f;
+    for (int k = D.tact_start[t]; k < D.tact_start[t + 1]; k++) { const int a = D.tact_list[k]; acc += D.act_gear[a] * sm[L.actforce + a]; }
+    sm[L.tforce + t] = acc;
+  }
+  __syncwarp();
+  for (int i = lane; i < nv; i += 32) {
+    float acc = 0.f;
+    for (int c = D.col_start[i]; c < D.col_start[i + 1]; c++) { const int n = D.col_nz[c]; acc += sm[L.tenJ + n] * sm[L.tforce + D.nz_tendon[n]]; }
+    for (int k = D.dact_start[i]; k < D.dact_start[i + 1]; k++) { const int a = D.dact_list[k]; acc += D.act_gear[a] * sm[L.actforce + a]; }
+    sm[L.qfrc_act + i] = acc;
+    sm[L.smooth + i] = sm[L.passive + i] - sm[L.bias + i] + acc;
+    sm[L.qacc_smooth + i] = sm[L.smooth + i];
+  }
+  __syncwarp();
+  solveLDL(D, sm + L.qLD, sm + L.qLDinv, sm + L.qacc_smooth, lane);
+  float* o;
+  if ((o = (float*)F.p[MYO_F_ACTUATOR_LENGTH])) for (int i = lane; i < nu; i += 32) o[w * nu + i] = sm[L.actlen + i];
+  if ((o = (float*)F.p[MYO_F_ACTUATOR_VELOCITY])) for (int i = lane; i < nu; i += 32) o[w * nu + i] = sm[L.actvel + i];
+  if ((o = (float*)F.p[MYO_F_ACTUATOR_FORCE])) for (int i = lane; i < nu; i += 32) o[w * nu + i] = sm[L.actforce + i];
+  if ((o = (float*)F.p[MYO_F_ACT_DOT])) for (int i = lane; i < D.na; i += 32) o[w * D.na + i] = sm[L.actdot + i];
+  if ((o = (float*)F.p[MYO_F_QFRC_ACTUATOR])) for (int i = lane; i < nv; i += 32) o[w * nv + i] = sm[L.qfrc_act + i];
+  if ((o = (float*)F.p[MYO_F_QFRC_SMOOTH])) for (int i = lane; i < nv; i += 32) o[w * nv + i] = sm[L.smooth + i];
+  if ((o = (float*)F.p[MYO_F_QACC_SMOOTH])) for (int i = lane; i < nv; i += 32) o[w * nv + i] = sm[L.qacc_smooth + i];
+  if ((o = (float*)F.p[MYO_F_ACTUATOR_MOMENT])) {
+    const size_t n = (size_t)nu * nv;
+    for (int i = lane; i < (int)n; i += 32) o[w * n + i] = 0.f;
+    __syncwarp();
+    for (int a = 0; a < nu; a++) {   // rows are sparse copies of the tendon rows
+      const int id = D.act_trnid[a];
+      if (D.act_trntype[a] == 3) { for (int k = D.ten_nzstart[id] + lane; k < D.ten_nzstart[id + 1]; k += 32) o[w * n + (size_t)a * nv + D.nz_dof[k]] = D.act_gear[a] * sm[L.tenJ + k]; }
+      else if (lane == 0) o[w * n + (size_t)a * nv + D.jnt_dofadr[id]] = D.act_gear[a];
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------ collision
+struct Shape { int type; f3 pos; const float* mat; f3 size; float margin; };
+__device__ f3 supportPt(const Shape& s, f3 dir) {
+  const f3 d = mulMT(s.mat, dir);
+  f3 r = mk3(0.f, 0.f, 0.f);
+  switch (s.type) {
+    case G_SPHERE: r = d * s.size.x; break;
+    case G_CAPSULE: r = d * s.size.x; r.z += d.z >= 0.f ? s.size.y : -s.size.y; break;
+    case G_ELLIPSOID: {
+      const f3 t = mk3(s.size.x * s.size.x * d.x, s.size.y * s.size.y * d.y, s.size.z * s.size.z * d.z);
+      r = t * rsqrtf(fmaxf(1e-30f, t.x * d.x + t.y * d.y + t.z * d.z));
+    } break;
+    case G_CYLINDER: {
+      const float n = sqrtf(d.x * d.x + d.y * d.y);
+      if (n > 1e-12f) { r.x = s.size.x * d.x / n; r.y = s.size.x * d.y / n; }
+      r.z = d.z >= 0.f ? s.size.y : -s.size.y;
+    } break;
+    case G_BOX: r = mk3(d.x >= 0.f ? s.size.x : -s.size.x, d.y >= 0.f ? s.size.y : -s.size.y, d.z >= 0.f ? s.size.z : -s.size.z); break;
+    default: break;
+  }
+  return mulM(s.mat, r) + s.pos + dir * s.margin;
+}
+struct Sup { f3 v, a, b; };
+__device__ __forceinline__ Sup mprSup(const Shape& A, const Shape& B, f3 d) {
+  Sup s; s.a = supportPt(A, d * -1.f); s.b = supportPt(B, d); s.v = s.b - s.a; return s;
+}
+// Minkowski portal refinement on B - A (same statement as oracle/mjstep_oracle.cpp, float32)
+__device__ bool mprPenetration(const Shape& A, const Shape& B, float tol, int maxit, float* depth, f3* nrm, f3* pos) {
+  f3 v0 = B.pos - A.pos;
+  if (norm3(v0) < 1e-12f) v0 = mk3(1e-5f, 0.f, 0.f);
+  f3 dir = unit3(v0 * -1.f);
+  Sup s1 = mprSup(A, B, dir);
+  if (dot(s1.v, dir) <= 0.f) return false;
+  dir = cross(s1.v, v0);
+  if (norm3(dir) < 1e-7f * fmaxf(1e-20f, norm3(s1.v) * norm3(v0))) {
+    const f3 n = unit3(s1.v - v0);
+    *depth = dot(s1.v, n); *nrm = n * -1.f; *pos = (s1.a + s1.b) * 0.5f;
+    return true;
+  }
+  dir = unit3(dir);
+  Sup s2 = mprSup(A, B, dir);
+  if (dot(s2.v, dir) <= 0.f) return false;
+  dir = unit3(cross(s1.v - v0, s2.v - v0));
+  if (dot(dir, v0) > 0.f) { Sup t = s1; s1 = s2; s2 = t; dir = dir * -1.f; }
+  Sup s3;
+  for (int it = 0;; it++) {
+    if (it > maxit) return false;
+    s3 = mprSup(A, B, dir);
+    if (dot(s3.v, dir) <= 0.f) return false;
+    if (dot(cross(s1.v, s3.v), v0) < 0.f) { s2 = s3; dir = unit3(cross(s1.v - v0, s3.v - v0)); continue; }
+    if (dot(cross(s3.v, s2.v), v0) < 0.f) { s1 = s3; dir = unit3(cross(s3.v - v0, s2.v - v0)); continue; }
+    break;
+  }
+  bool hit = false;
+  for (int it = 0;; it++) {
+    dir = unit3(cross(s2.v - s1.v, s3.v - s1.v));
+    if (dot(dir, s1.v) >= 0.f) hit = true;
+    const Sup s4 = mprSup(A, B, dir);
+    if (dot(s4.v, dir) < 0.f && !hit) return false;
+    const float adv = fminf(fminf(dot(s4.v - s1.v, dir), dot(s4.v - s2.v, dir)), dot(s4.v - s3.v, dir));
+    if (adv <= tol || it >= maxit) {
+      if (!hit) return false;
+      const float d = dot(dir, s1.v);
+      const f3 p = dir * d, e0 = s2.v - s1.v, e1 = s3.v - s1.v, e2 = p - s1.v;
+      const float d00 = dot(e0, e0), d01 = dot(e0, e1), d11 = dot(e1, e1), d20 = dot(e2, e0), d21 = dot(e2, e1);
+      const float den = d00 * d11 - d01 * d01;
+      float b1 = 1.f, b2 = 0.f, b3 = 0.f;
+      if (fabsf(den) > 1e-30f) { b2 = (d11 * d20 - d01 * d21) / den; b3 = (d00 * d21 - d01 * d20) / den; b1 = 1.f - b2 - b3; }
+      b1 = clipf(b1, 0.f, 1.f); b2 = clipf(b2, 0.f, 1.f); b3 = clipf(b3, 0.f, 1.f);
+      const float bs = 1.f / fmaxf(1e-30f, b1 + b2 + b3);
+      const f3 pa = (s1.a * b1 + s2.a * b2 + s3.a * b3) * bs, pb = (s1.b * b1 + s2.b * b2 + s3.b * b3) * bs;
+      *depth = d; *nrm = dir * -1.f; *pos = (pa + pb) * 0.5f;
+      return true;
+    }
+    const f3 c = cross(s4.v, v0);
+    if (dot(s1.v, c) > 0.f) { if (dot(s2.v, c) > 0.f) s1 = s4; else s3 = s4; }
+    else { if (dot(s3.v, c) > 0.f) s2 = s4; else s1 = s4; }
+  }
+}
+struct Hit { float dist; f3 pos, nrm; };
+__device__ __forceinline__ Hit sphereSphere(f3 c1, float r1, f3 c2, float r2) {
+  const f3 d = c2 - c1; const float n = norm3(d);
+  Hit h; h.nrm = n < MINVAL ? mk3(1.f, 0.f, 0.f) : d * (1.f / n);
+  h.dist = n - r1 - r2; h.pos = c1 + h.nrm * (r1 + 0.5f * h.dist);
+  return h;
+}
+// narrow phase for one candidate pair; returns the number of contacts (0..2) with dist < margin
+__device__ int collidePair(const DevModel& D, const SmemLayout& L, const float* sm, int pr, Hit* h) {
+  const int c1 = D.pair_cg1[pr], c2 = D.pair_cg2[pr];
+  const int t1 = D.cg_type[c1], t2 = D.cg_type[c2];
+  const float margin = D.pair_prm[16 * pr];
+  const float* P1 = sm + L.cgpose + 12 * c1; const float* P2 = sm + L.cgpose + 12 * c2;
+  const f3 p1 = ld3(P1), p2 = ld3(P2);
+  const float *R1 = P1 + 3, *R2 = P2 + 3;
+  const f3 sz1 = ld3(D.cg_size + 3 * c1), sz2 = ld3(D.cg_size + 3 * c2);
+  const f3 ax1 = mk3(R1[2], R1[5], R1[8]), ax2 = mk3(R2[2], R2[5], R2[8]);
+  int n = 0;
+  if (t1 == G_PLANE) {
+    if (dot(p2 - p1, ax1) > D.cg_rbound[c2] + margin) return 0;
+    if (t2 == G_SPHERE || t2 == G_CAPSULE) {
+      const int cnt = t2 == G_SPHERE ? 1 : 2;
+      for (int k = 0; k < cnt; k++) {
+        const f3 c = t2 == G_SPHERE ? p2 : (k == 0 ? p2 + ax2 * sz2.y : p2 - ax2 * sz2.y);
+        const float dist = dot(c - p1, ax1) - sz2.x;
+        if (dist < margin) { h[n].dist = dist; h[n].pos = c - ax1 * (sz2.x + 0.5f * dist); h[n].nrm = ax1; n++; }
+      }
+    } else {
+      Shape s; s.type = t2; s.pos = p2; s.mat = R2; s.size = sz2; s.margin = 0.f;
+      const f3 sp = supportPt(s, ax1 * -1.f);
+      const float dist = dot(sp - p1, ax1);
+      if (dist < margin) { h[0].dist = dist; h[0].pos = sp - ax1 * (0.5f * dist); h[0].nrm = ax1; n = 1; }
+    }
+    return n;
+  }
+  if (norm3(p2 - p1) > D.cg_rbound[c1] + D.cg_rbound[c2] + margin) return 0;
+  if (t1 == G_SPHERE && t2 == G_SPHERE) h[0] = sphereSphere(p1, sz1.x, p2, sz2.x);
+  else if (t1 == G_SPHERE && t2 == G_CAPSULE) h[0] = sphereSphere(p1, sz1.x, p2 + ax2 * clipf(dot(p1 - p2, ax2), -sz2.y, sz2.y), sz2.x);
+  else if (t1 == G_CAPSULE && t2 == G_CAPSULE) {
+    const f3 a1 = ax1 * sz1.y, a2 = ax2 * sz2.y, dif = p1 - p2;
+    const float ma = dot(a1, a1), mb = -dot(a1, a2), mc = dot(a2, a2), u = -dot(a1, dif), v = dot(a2, dif);
+    const float det = ma * mc - mb * mb;
+    float x1, x2;
+    if (fabsf(det) >= 1e-30f) {
+      x1 = (mc * u - mb * v) / det; x2 = (ma * v - mb * u) / det;
+      if (x1 > 1.f) { x1 = 1.f; x2 = (v - mb) / mc; } else if (x1 < -1.f) { x1 = -1.f; x2 = (v + mb) / mc; }
+      if (x2 > 1.f) { x2 = 1.f; x1 = clipf((u - mb) / ma, -1.f, 1.f); } else if (x2 < -1.f) { x2 = -1.f; x1 = clipf((u + mb) / ma, -1.f, 1.f); }
+    } else {
+      x1 = clipf(u / fmaxf(1e-30f, ma), -1.f, 1.f);
+      x2 = clipf((v - mb * x1) / fmaxf(1e-30f, mc), -1.f, 1.f);
+    }
+    h[0] = sphereSphere(p1 + a1 * x1, sz1.x, p2 + a2 * x2, sz2.x);
+  } else {
+    Shape A, B;
+    A.type = t1; A.pos = p1; A.mat = R1; A.size = sz1; A.margin = 0.5f * margin;
+    B.type = t2; B.pos = p2; B.mat = R2; B.size = sz2; B.margin = 0.5f * margin;
+    float depth; f3 nrm, pos;
+    if (!mprPenetration(A, B, 1e-6f, 50, &depth, &nrm, &pos)) return 0;
+    h[0].dist = margin - depth; h[0].pos = pos; h[0].nrm = nrm;
+  }
+  return h[0].dist < margin ? 1 : 0;
+}
+__device__ __forceinline__ void makeFrame(f3 n, f3* y, f3* z) {
+  f3 t = mk3(0.f, 0.f, 0.f);
+  if (n.y < 0.5f && n.y > -0.5f) t.y = 1.f; else t.z = 1.f;
+  t = unit3(t - n * dot(n, t));
+  *y = t; *z = cross(n, t);
+}
+// returns the number of contacts; contact record: dist, pos[3], normal[3], pair, efc_address, dim, spare[2]
+__device__ int collision(const DevModel& D, const SmemLayout& L, float* sm, int lane, int* status) {
+  if (D.npair == 0) return 0;
+  for (int c = lane; c < D.ncg; c += 32) {
+    const int f = D.cg_frame[c];
+    const float* R = FR_MAT(sm, L, f); const float* lm = D.cg_lmat + 9 * c;
+    float* o = sm + L.cgpose + 12 * c;
+    st3(o, ld3(FR_POS(sm, L, f)) + mulM(R, ld3(D.cg_lpos + 3 * c)));
+#pragma unroll
+    for (int i = 0; i < 3; i++)
+#pragma unroll
+      for (int j = 0; j < 3; j++) o[3 + 3 * i + j] = R[3 * i] * lm[j] + R[3 * i + 1] * lm[3 + j] + R[3 * i + 2] * lm[6 + j];
+  }
+  __syncwarp();
+  int ncon = 0;
+  for (int base = 0; base < D.npair; base += 32) {
+    const int pr = base + lane;
+    Hit h[2]; int n = 0;
+    if (pr < D.npair) n = collidePair(D, L, sm, pr, h);
+    // exclusive scan of the per-lane contact counts keeps the pair order
+    int incl = n;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(FULLMASK, incl, o); if (lane >= o) incl += t; }
+    const int total = __shfl_sync(FULLMASK, incl, 31);
+    int at = ncon + incl - n;
+    for (int k = 0; k < n; k++, at++) {
+      if (at >= D.nconmax) continue;
+      float* c = sm + L.con + 12 * at;
+      c[0] = h[k].dist; st3(c + 1, h[k].pos); st3(c + 4, h[k].nrm);
+      c[7] = __int_as_float(pr); c[8] = __int_as_float(-1); c[9] = __int_as_float(D.pair_dim[pr]);
+    }
+    ncon += total;
+  }
+  if (ncon > D.nconmax) { *status |= MYO_WORLD_NCON_OVERFLOW; ncon = D.nconmax; }
+  __syncwarp();
+  return ncon;
+}
+
+// ------------------------------------------------------------------------------------------ constraints
+enum { E_D = 0, E_AREF, E_JAR, E_JV, E_FORCE, E_DESC0, E_COEF, E_DESC1, E_POS, E_MARGIN };
+#define EFC(k, r) sm[L.efc + (k) * D.njmax + (r)]
+#define EFCI(k, r) __float_as_int(sm[L.efc + (k) * D.njmax + (r)])
+
+__device__ __forceinline__ float impedance(const float* si, float x) {  // si = sanitised solimp, x = |pos - margin|
+  const float dmin = si[0], dmax = si[1], width = si[2], mid = si[3], power = si[4];
+  if (dmin == dmax || width <= MINVAL) return 0.5f * (dmin + dmax);
+  x = x / width;
+  if (x >= 1.f) return dmax;
+  if (x <= 0.f) return dmin;
+  float y;
+  if (power == 1.f) y = x;
+  else if (x <= mid) y = powf(x, power) / powf(mid, power - 1.f);
+  else y = 1.f - powf(1.f - x, power) / powf(1.f - mid, power - 1.f);
+  return dmin + y * (dmax - dmin);
+}
+__device__ __forceinline__ void setRow(const DevModel& D, const SmemLayout& L, float* sm, int r, int type, int id, float coef, int desc1,
+                                       float pos, float margin, float dA, const float* kb, float vel, float Rscale) {
+  // kb: K, B, solimp[5]
+  const float imp = impedance(kb + 2, fabsf(pos - margin));
+  float R = fmaxf(MINVAL, (1.f - imp) * dA / imp);
+  if (Rscale > 0.f) R = fmaxf(MINVAL, Rscale * R);
+  EFC(E_D, r) = 1.f / R;
+  EFC(E_AREF, r) = -kb[1] * vel - kb[0] * imp * (pos - margin);
+  EFC(E_DESC0, r) = __int_as_float(type | (id << 2)); EFC(E_COEF, r) = coef; EFC(E_DESC1, r) = __int_as_float(desc1);
+  EFC(E_POS, r) = pos; EFC(E_MARGIN, r) = margin; EFC(E_FORCE, r) = 0.f;
+}
+__device__ __forceinline__ int warpExclScan(int v, int lane, int* total) {
+  int incl = v;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(FULLMASK, incl, o); if (lane >= o) incl += t; }
+  *total = __shfl_sync(FULLMASK, incl, 31);
+  return incl - v;
+}
+// base-row products  out[b] = conJ[b] . x   for the nb*ncon contact base rows
+__device__ __forceinline__ void baseMul(const DevModel& D, const SmemLayout& L, float* sm, int lane, int ncon, const float* x, float* out) {
+  const int nbr = D.maxbase * ncon, nv = D.nv;
+  for (int b = lane; b < nbr; b += 32) {
+    const float* J = sm + L.conJ + b * nv;
+    float acc = 0.f;
+    for (int k = 0; k < nv; k++) acc = fmaf(J[k], x[k], acc);
+    out[b] = acc;
+  }
+}
+// out[r] = J_r . x for every efc row (bx = base products of x)
+__device__ __forceinline__ float rowMul(const DevModel& D, const SmemLayout& L, const float* sm, int r, const float* x, const float* bx) {
+  const int d0 = EFCI(E_DESC0, r), type = d0 & 3, id = d0 >> 2;
+  const float coef = EFC(E_COEF, r);
+  if (type == ROW_LIMJ) return coef * x[D.limj_dof[id]];
+  if (type == ROW_CON) { const int t = EFCI(E_DESC1, r); return bx[id] + (t >= 0 ? coef * bx[t] : 0.f); }
+  if (type == ROW_EQ) { const int d2 = D.eq_dof2[id]; return x[D.eq_dof1[id]] + (d2 >= 0 ? coef * x[d2] : 0.f); }
+  const int t = D.limt_ten[id];
+  float acc = 0.f;
+  for (int n = D.ten_nzstart[t]; n < D.ten_nzstart[t + 1]; n++) acc += sm[L.tenJ + n] * x[D.nz_dof[n]];
+  return coef * acc;
+}
+
+__device__ int makeConstraint(const DevModel& D, const SmemLayout& L, float* sm, int lane, int ncon, int* status) {
+  const int nv = D.nv, njmax = D.njmax;
+  const float* qpos = sm + L.qpos; const float* qvel = sm + L.qvel;
+  int nefc = 0;
+  if (D.disableflags & DSBL_CONSTRAINT) return 0;
+  // ---- equality rows (always active)
+  for (int e = lane; e < D.neq; e += 32) {
+    const int d1 = D.eq_dof1[e], d2 = D.eq_dof2[e], q1 = D.eq_q1[e], q2 = D.eq_q2[e];
+    const float* dt = D.eq_data + 5 * e;
+    float pos, dpoly = 0.f, vel = qvel[d1];
+    if (d2 >= 0) {
+      const float x = qpos[q2] - D.qpos0[q2];
+      pos = qpos[q1] - D.qpos0[q1] - (dt[0] + x * (dt[1] + x * (dt[2] + x * (dt[3] + x * dt[4]))));
+      dpoly = dt[1] + x * (2.f * dt[2] + x * (3.f * dt[3] + x * 4.f * dt[4]));
+      vel -= dpoly * qvel[d2];
+    } else pos = qpos[q1] - D.qpos0[q1] - dt[0];
+    setRow(D, L, sm, e, ROW_EQ, e, -dpoly, 0, pos, 0.f, D.eq_prm[8 * e + 7], D.eq_prm + 8 * e, vel, 0.f);
+  }
+  nefc = D.neq;
+  // ---- joint limits, then tendon limits
+  const int nlim = D.nlimj + D.nlimt;
+  for (int base = 0; base < nlim; base += 32) {
+    const int li = base + lane;
+    float dlo = 1.f, dhi = 1.f, margin = 0.f; int cnt = 0;
+    const bool isj = li < D.nlimj;
+    const float* prm = nullptr;
+    if (li < nlim) {
+      prm = isj ? D.limj_prm + 12 * li : D.limt_prm + 12 * (li - D.nlimj);
+      const float val = isj ? qpos[D.limj_q[li]] : sm[L.tenlen + D.limt_ten[li - D.nlimj]];
+      margin = prm[2]; dlo = val - prm[0]; dhi = prm[1] - val;
+      cnt = (dlo < margin) + (dhi < margin);
+    }
+    int total; int at = nefc + warpExclScan(cnt, lane, &total);
+    if (li < nlim) {
+      int r0 = -1, r1 = -1;
+      const float v = isj ? qvel[D.limj_dof[li]] : sm[L.tenvel + D.limt_ten[li - D.nlimj]];
+      const int id = isj ? li : li - D.nlimj, type = isj ? ROW_LIMJ : ROW_LIMT;
+      if (dlo < margin) { if (at < njmax) { r0 = at; setRow(D, L, sm, at, type, id, 1.f, 0, dlo, margin, prm[10], prm + 3, v, 0.f); } at++; }
+      if (dhi < margin) { if (at < njmax) { r1 = at; setRow(D, L, sm, at, type, id, -1.f, 0, dhi, margin, prm[10], prm + 3, -v, 0.f); } at++; }
+      sm[L.limrow + 2 * li] = __int_as_float(r0); sm[L.limrow + 2 * li + 1] = __int_as_float(r1);
+    }
+    nefc += total;
+  }
+  // ---- contacts: rows per contact, base Jacobians, pyramid rows
+  if (ncon > 0) {
+    const int nb = D.maxbase;
+    int adr_of_lane = -1;
+    for (int base = 0; base < ncon; base += 32) {   // nconmax may exceed 32
+      const int c = base + lane;
+      int rows = 0;
+      if (c < ncon) {
+        const float* cr = sm + L.con + 12 * c;
+        const int pr = __float_as_int(cr[7]), dim = __float_as_int(cr[9]);
+        const float inc = D.pair_prm[16 * pr] - D.pair_prm[16 * pr + 1];
+        if (cr[0] < inc) rows = dim == 1 ? 1 : 2 * (dim - 1);
+      }
+      int total; const int at = nefc + warpExclScan(rows, lane, &total);
+      if (c < ncon) { adr_of_lane = (rows > 0 && at + rows <= njmax) ? at : -1; sm[L.con + 12 * c + 8] = __int_as_float(adr_of_lane); }
+      nefc += total;
+    }
+    __syncwarp();
+    // base Jacobian rows, one contact at a time, lanes over dofs
+    for (int c = 0; c < ncon; c++) {
+      const float* cr = sm + L.con + 12 * c;
+      const int pr = __float_as_int(cr[7]);
+      const int f1 = D.cg_frame[D.pair_cg1[pr]], f2 = D.cg_frame[D.pair_cg2[pr]];
+      const f3 pos = ld3(cr + 1), n = ld3(cr + 4);
+      f3 y, z; makeFrame(n, &y, &z);
+      for (int k = lane; k < nv; k += 32) {
+        const int in1 = (D.fr_mask[2 * f1 + (k >> 5)] >> (k & 31)) & 1, in2 = (D.fr_mask[2 * f2 + (k >> 5)] >> (k & 31)) & 1;
+        const float s = (float)(in2 - in1);
+        f3 jp = mk3(0.f, 0.f, 0.f), jr = jp;
+        if (in1 != in2) {
+          const float* cd = sm + L.cdof + 6 * k;
+          jr = ld3(cd) * s;
+          jp = (ld3(cd + 3) + cross(ld3(cd), pos - ld3(sm + L.rootcom + 3 * D.fr_root[D.dof_frame[k]]))) * s;
+        }
+        float* J = sm + L.conJ + (c * nb) * nv + k;
+        J[0] = dot(n, jp);
+        if (nb > 1) { J[nv] = dot(y, jp); J[2 * nv] = dot(z, jp); }
+        if (nb > 3) J[3 * nv] = dot(n, jr);
+      }
+    }
+    __syncwarp();
+    float* bx = sm + L.basev;
+    baseMul(D, L, sm, lane, ncon, qvel, bx);
+    __syncwarp();
+    for (int c = lane; c < ncon; c += 32) {
+      const float* cr = sm + L.con + 12 * c;
+      const int adr = __float_as_int(cr[8]);
+      if (adr < 0) continue;
+      const int pr = __float_as_int(cr[7]), dim = __float_as_int(cr[9]);
+      const float* pp = D.pair_prm + 16 * pr;
+      const float margin = pp[0] - pp[1], dist = cr[0];
+      const int c1 = D.pair_cg1[pr], c2 = D.pair_cg2[pr];
+      const float tran = D.cg_invweight[2 * c1] + D.cg_invweight[2 * c2];
+      float kb[7] = {pp[14], pp[15], pp[9], pp[10], pp[11], pp[12], pp[13]};
+      const int bn = c * nb;
+      if (dim == 1) setRow(D, L, sm, adr, ROW_CON, bn, 0.f, -1, dist, margin, tran, kb, bx[bn], 0.f);
+      else {
+        const float mu0 = pp[2] * rsqrtf(D.impratio);
+        const float dA0 = tran + pp[2] * pp[2] * tran;   // first pyramid row sets the shared regulariser
+        for (int k = 1; k < dim; k++) {
+          const float mu = pp[1 + k];
+          const int bt = bn + k;
+          setRow(D, L, sm, adr + 2 * (k - 1), ROW_CON, bn, mu, bt, dist, margin, dA0, kb, bx[bn] + mu * bx[bt], 2.f * mu0 * mu0);
+          setRow(D, L, sm, adr + 2 * (k - 1) + 1, ROW_CON, bn, -mu, bt, dist, margin, dA0, kb, bx[bn] - mu * bx[bt], 2.f * mu0 * mu0);
+        }
+      }
+    }
+  }
+  if (nefc > njmax) { *status |= MYO_WORLD_NEFC_OVERFLOW; nefc = njmax; }
+  __syncwarp();
+  return nefc;
+}
+
+// ------------------------------------------------------------------------------------------ Newton solver (mj_fwdConstraint)
+__device__ __forceinline__ void mulMsparse(const DevModel& D, const float* qM, const float* x, float* out, int lane) {
+  for (int i = lane; i < D.nv; i += 32) {
+    const int a = D.dof_Madr[i], d = D.dof_rowlen[i];
+    float acc = 0.f;
+    for (int s = 0; s < d; s++) acc = fmaf(qM[a + s], x[D.M_col[a + s]], acc);
+    for (int e = D.desc_start[i]; e < D.desc_start[i + 1]; e++) acc = fmaf(qM[D.desc_idx[e]], x[D.desc_dof[e]], acc);
+    out[i] = acc;
+  }
+}
+// jar = J x - aref for all rows, returns (uniform) constraint cost; force/active are implied by jar
+__device__ float residualCost(const DevModel& D, const SmemLayout& L, float* sm, int lane, int ncon, int nefc, const float* x) {
+  float* bx = sm + L.basev;
+  baseMul(D, L, sm, lane, ncon, x, bx);
+  __syncwarp();
+  float cost = 0.f;
+  for (int r = lane; r < nefc; r += 32) {
+    const float jar = rowMul(D, L, sm, r, x, bx) - EFC(E_AREF, r);
+    EFC(E_JAR, r) = jar;
+    const bool on = ((EFCI(E_DESC0, r) & 3) == ROW_EQ) || jar < 0.f;
+    if (on) cost += 0.5f * EFC(E_D, r) * jar * jar;
+  }
+  __syncwarp();
+  return warpSum(cost);
+}
+__device__ __forceinline__ bool rowActive(const DevModel& D, const SmemLayout& L, const float* sm, int r) {
+  return ((EFCI(E_DESC0, r) & 3) == ROW_EQ) || EFC(E_JAR, r) < 0.f;
+}
+// forces from jar, then out = J^T f  (deterministic gathers, no atomics)
+__device__ void constraintForce(const DevModel& D, const SmemLayout& L, float* sm, int lane, int ncon, int nefc, float* out) {
+  const int nv = D.nv, nb = D.maxbase;
+  for (int r = lane; r < nefc; r += 32) EFC(E_FORCE, r) = rowActive(D, L, sm, r) ? -EFC(E_D, r) * EFC(E_JAR, r) : 0.f;
+  __syncwarp();
+  float* bf = sm + L.basev + nb * D.nconmax;
+  for (int b = lane; b < nb * ncon; b += 32) {
+    const int c = b / nb, k = b - c * nb;
+    const float* cr = sm + L.con + 12 * c;
+    const int adr = __float_as_int(cr[8]), dim = __float_as_int(cr[9]);
+    float f = 0.f;
+    if (adr >= 0 && k < dim) {
+      if (dim == 1) f = EFC(E_FORCE, adr);
+      else if (k == 0) { for (int p = 0; p < 2 * (dim - 1); p++) f += EFC(E_FORCE, adr + p); }
+      else f = EFC(E_COEF, adr + 2 * (k - 1)) * (EFC(E_FORCE, adr + 2 * (k - 1)) - EFC(E_FORCE, adr + 2 * (k - 1) + 1));
+    }
+    bf[b] = f;
+  }
+  __syncwarp();
+  for (int k = lane; k < nv; k += 32) {
+    float acc = 0.f;
+    for (int e = D.dofeq_start[k]; e < D.dofeq_start[k + 1]; e++) {
+      const int v = D.dofeq_list[e], r = v >> 1;
+      acc += (v & 1) ? EFC(E_COEF, r) * EFC(E_FORCE, r) : EFC(E_FORCE, r);
+    }
+    const int li = D.dof_limidx[k];
+    if (li >= 0)
+      for (int s = 0; s < 2; s++) { const int r = __float_as_int(sm[L.limrow + 2 * li + s]); if (r >= 0) acc += EFC(E_COEF, r) * EFC(E_FORCE, r); }
+    if (D.nlimt > 0)
+      for (int c = D.col_start[k]; c < D.col_start[k + 1]; c++) {
+        const int n = D.col_nz[c], lt = D.ten_limidx[D.nz_tendon[n]];
+        if (lt < 0) continue;
+        for (int s = 0; s < 2; s++) {
+          const int r = __float_as_int(sm[L.limrow + 2 * (D.nlimj + lt) + s]);
+          if (r >= 0) acc += EFC(E_COEF, r) * EFC(E_FORCE, r) * sm[L.tenJ + n];
+        }
+      }
+    for (int b = 0; b < nb * ncon; b++) acc = fmaf(sm[L.conJ + b * nv + k], bf[b], acc);
+    out[k] = acc;
+  }
+  __syncwarp();
+}
+// H = M + J^T D_active J (lower triangle), Cholesky in place
+__device__ void hessianFactor(const DevModel& D, const SmemLayout& L, float* sm, int lane, int ncon, int nefc) {
+  const int nv = D.nv, nb = D.maxbase;
+  float* H = sm + L.H;
+  for (int i = lane; i < nv * nv; i += 32) H[i] = 0.f;
+  __syncwarp();
+  for (int e = lane; e < D.nM; e += 32) H[D.M_row[e] * nv + D.M_col[e]] = sm[L.qM + e];
+  __syncwarp();
+  for (int k = lane; k < nv; k += 32) {
+    const int li = D.dof_limidx[k];
+    if (li < 0) continue;
+    for (int s = 0; s < 2; s++) { const int r = __float_as_int(sm[L.limrow + 2 * li + s]); if (r >= 0 && rowActive(D, L, sm, r)) H[k * nv + k] += EFC(E_D, r); }
+  }
+  __syncwarp();
+  for (int e = 0; e < D.neq; e++) {
+    const int d1 = D.eq_dof1[e], d2 = D.eq_dof2[e];
+    const float Dr = EFC(E_D, e), c = EFC(E_COEF, e);
+    if (lane == 0) H[d1 * nv + d1] += Dr;
+    if (lane == 1 && d2 >= 0) H[max(d1, d2) * nv + min(d1, d2)] += Dr * c;
+    if (lane == 2 && d2 >= 0) H[d2 * nv + d2] += Dr * c * c;
+    __syncwarp();
+  }
+  for (int lt = 0; lt < D.nlimt; lt++)
+    for (int s = 0; s < 2; s++) {
+      const int r = __float_as_int(sm[L.limrow + 2 * (D.nlimj + lt) + s]);
+      if (r < 0 || !rowActive(D, L, sm, r)) continue;
+      const int t = D.limt_ten[lt], n0 = D.ten_nzstart[t], cnt = D.ten_nzstart[t + 1] - n0;
+      const float Dr = EFC(E_D, r);
+      for (int i = lane; i < cnt * cnt; i += 32) {
+        const int a = i / cnt, b = i - a * cnt;
+        const int da = D.nz_dof[n0 + a], db = D.nz_dof[n0 + b];
+        if (da >= db) H[da * nv + db] += Dr * sm[L.tenJ + n0 + a] * sm[L.tenJ + n0 + b];
+      }
+      __syncwarp();
+    }
+  for (int c = 0; c < ncon; c++) {
+    const float* cr = sm + L.con + 12 * c;
+    const int adr = __float_as_int(cr[8]), dim = __float_as_int(cr[9]);
+    if (adr < 0) continue;
+    // weights in base-row space: W = sum_p D_p w_p w_p^T, w_p = e_n +- mu e_t
+    float Wnn = 0.f, Wnt[3] = {0.f, 0.f, 0.f}, Wtt[3] = {0.f, 0.f, 0.f};
+    if (dim == 1) { if (rowActive(D, L, sm, adr)) Wnn = EFC(E_D, adr); }
+    else
+      for (int k = 1; k < dim; k++) {
+        const int r0 = adr + 2 * (k - 1);
+        const float mu = EFC(E_COEF, r0);
+        const float Dp = rowActive(D, L, sm, r0) ? EFC(E_D, r0) : 0.f, Dm = rowActive(D, L, sm, r0 + 1) ? EFC(E_D, r0 + 1) : 0.f;
+        Wnn += Dp + Dm; Wnt[k - 1] = mu * (Dp - Dm); Wtt[k - 1] = mu * mu * (Dp + Dm);
+      }
+    if (Wnn == 0.f) continue;
+    const float* Jn = sm + L.conJ + (c * nb) * nv;
+    for (int i = lane; i < nv * nv; i += 32) {
+      const int r = i / nv, cc = i - r * nv;
+      if (cc > r) continue;
+      float acc = Wnn * Jn[r] * Jn[cc];
+      for (int k = 1; k < dim; k++) {
+        const float* Jt = Jn + k * nv;
+        acc += Wnt[k - 1] * (Jn[r] * Jt[cc] + Jt[r] * Jn[cc]) + Wtt[k - 1] * Jt[r] * Jt[cc];
+      }
+      H[i] += acc;
+    }
+    __syncwarp();
+  }
+  // left-looking Cholesky, lanes over rows
+  for (int j = 0; j < nv; j++) {
+    float sj = 0.f;
+    for (int r = j + lane; r < nv; r += 32) {
+      float s = H[r * nv + j];
+      for (int k = 0; k < j; k++) s = fmaf(-H[r * nv + k], H[j * nv + k], s);
+      if (r == j) sj = s; else H[r * nv + j] = s;
+    }
+    sj = __shfl_sync(FULLMASK, sj, 0);
+    const float d = sqrtf(fmaxf(sj, MINVAL)), inv = 1.f / d;
+    __syncwarp();
+    for (int r = j + lane; r < nv; r += 32) { if (r == j) H[j * nv + j] = d; else H[r * nv + j] *= inv; }
+    __syncwarp();
+  }
+}
+__device__ void cholSolve(const DevModel& D, const float* H, float* x, int lane) {
+  const int nv = D.nv;
+  for (int j = 0; j < nv; j++) {
+    const float xj = x[j] / H[j * nv + j];
+    __syncwarp();
+    if (lane == 0) x[j] = xj;
+    for (int r = j + 1 + lane; r < nv; r += 32) x[r] = fmaf(-H[r * nv + j], xj, x[r]);
+    __syncwarp();
+  }
+  for (int j = nv - 1; j >= 0; j--) {
+    const float xj = x[j] / H[j * nv + j];
+    __syncwarp();
+    if (lane == 0) x[j] = xj;
+    for (int r = lane; r < j; r += 32) x[r] = fmaf(-H[j * nv + r], xj, x[r]);
+    __syncwarp();
+  }
+}
+struct LsPt { float alpha, cost, d0, d1; };
+__device__ __forceinline__ LsPt lsEval(const DevModel& D, const SmemLayout& L, const float* sm, int lane, int nefc, float a, const float* qg) {
+  float q0 = 0.f, q1 = 0.f, q2 = 0.f;
+  for (int r = lane; r < nefc; r += 32) {
+    const float jar = EFC(E_JAR, r), jv = EFC(E_JV, r), x = jar + a * jv;
+    if (((EFCI(E_DESC0, r) & 3) == ROW_EQ) || x < 0.f) {
+      const float Dr = EFC(E_D, r);
+      q0 += 0.5f * Dr * jar * jar; q1 += Dr * jar * jv; q2 += 0.5f * Dr * jv * jv;
+    }
+  }
+  q0 = warpSum(q0) + qg[0]; q1 = warpSum(q1) + qg[1]; q2 = warpSum(q2) + qg[2];
+  LsPt p; p.alpha = a; p.cost = a * a * q2 + a * q1 + q0; p.d0 = 2.f * a * q2 + q1; p.d1 = 2.f * q2;
+  if (p.d1 <= 0.f) p.d1 = MINVAL;
+  return p;
+}
+__device__ int solveNewton(const DevModel& D, const SmemLayout& L, float* sm, int lane, int ncon, int nefc, int* status) {
+  const int nv = D.nv;
+  float* qacc = sm + L.qacc; float* Ma = sm + L.nvec; float* grad = Ma + nv; float* search = grad + nv; float* Mv = search + nv;
+  float* tmp = Mv + nv;
+  const float* smooth = sm + L.smooth; const float* qas = sm + L.qacc_smooth;
+  // warm start: cheaper of qacc_warmstart and qacc_smooth
+  float costW = 3.4e38f;
+  if (!(D.disableflags & DSBL_WARMSTART)) {
+    mulMsparse(D, sm + L.qM, sm + L.warm, Ma, lane);
+    __syncwarp();
+    float g = 0.f;
+    for (int k = lane; k < nv; k += 32) g += 0.5f * (Ma[k] - smooth[k]) * (sm[L.warm + k] - qas[k]);
+    costW = warpSum(g) + residualCost(D, L, sm, lane, ncon, nefc, sm + L.warm);
+  }
+  const float costS = residualCost(D, L, sm, lane, ncon, nefc, qas);
+  const bool useWarm = !(costW > costS);
+  for (int k = lane; k < nv; k += 32) qacc[k] = useWarm ? sm[L.warm + k] : qas[k];
+  __syncwarp();
+  mulMsparse(D, sm + L.qM, qacc, Ma, lane);
+  __syncwarp();
+  float gauss = 0.f;
+  for (int k = lane; k < nv; k += 32) gauss += 0.5f * (Ma[k] - smooth[k]) * (qacc[k] - qas[k]);
+  gauss = warpSum(gauss);
+  float cost = gauss + residualCost(D, L, sm, lane, ncon, nefc, qacc);
+  const float scale = 1.f / (D.meaninertia * (float)max(1, nv));
+  int iter = 0;
+  for (;;) {
+    // gradient, Hessian, Newton direction
+    constraintForce(D, L, sm, lane, ncon, nefc, tmp);
+    float gn = 0.f;
+    for (int k = lane; k < nv; k += 32) { const float g = Ma[k] - smooth[k] - tmp[k]; grad[k] = g; search[k] = g; gn += g * g; }
+    gn = sqrtf(warpSum(gn));
+    if (iter > 0 && scale * gn < D.tolerance) break;
+    if (iter >= D.iterations) { *status |= MYO_WORLD_SOLVER_MAXITER; break; }
+    __syncwarp();
+    hessianFactor(D, L, sm, lane, ncon, nefc);
+    cholSolve(D, sm + L.H, search, lane);
+    float sn = 0.f;
+    for (int k = lane; k < nv; k += 32) { const float s = -search[k]; search[k] = s; sn += s * s; }
+    sn = sqrtf(warpSum(sn));
+    __syncwarp();
+    if (sn < MINVAL) break;
+    // exact line search along `search`
+    mulMsparse(D, sm + L.qM, search, Mv, lane);
+    float* bx = sm + L.basev;
+    baseMul(D, L, sm, lane, ncon, search, bx);
+    __syncwarp();
+    for (int r = lane; r < nefc; r += 32) EFC(E_JV, r) = rowMul(D, L, sm, r, search, bx);
+    float g1 = 0.f, g2 = 0.f;
+    for (int k = lane; k < nv; k += 32) { g1 += search[k] * (Ma[k] - smooth[k]); g2 += 0.5f * search[k] * Mv[k]; }
+    __syncwarp();
+    const float qg[3] = {gauss, warpSum(g1), warpSum(g2)};
+    const float gtol = D.tolerance * D.ls_tolerance * sn / scale;
+    int lsiter = 0;
+    LsPt p0 = lsEval(D, L, sm, lane, nefc, 0.f, qg); lsiter++;
+    LsPt p1 = lsEval(D, L, sm, lane, nefc, p0.alpha - p0.d0 / p0.d1, qg); lsiter++;
+    if (p0.cost < p1.cost) p1 = p0;
+    bool done = fabsf(p1.d0) < gtol;
+    if (!done) {
+      const float dir = p1.d0 < 0.f ? 1.f : -1.f;
+      LsPt p2 = p1; bool have2 = false;
+      while (p1.d0 * dir <= -gtol && lsiter < D.ls_iterations) {
+        p2 = p1; have2 = true;
+        p1 = lsEval(D, L, sm, lane, nefc, p1.alpha - p1.d0 / p1.d1, qg); lsiter++;
+        if (fabsf(p1.d0) < gtol) { done = true; break; }
+      }
+      if (!done && lsiter < D.ls_iterations && have2) {
+        LsPt lo = p2, hi = p1;
+        while (lsiter < D.ls_iterations) {
+          bool moved = false;
+          LsPt best = lo.cost < hi.cost ? lo : hi;
+          const float ca[3] = {lo.alpha - lo.d0 / lo.d1, hi.alpha - hi.d0 / hi.d1, 0.5f * (lo.alpha + hi.alpha)};
+          LsPt cand[3];
+#pragma unroll
+          for (int q = 0; q < 3; q++) { cand[q] = lsEval(D, L, sm, lane, nefc, ca[q], qg); lsiter++; }
+#pragma unroll
+          for (int q = 0; q < 3; q++) {
+            if (done) break;
+            const LsPt c = cand[q];
+            if (fabsf(c.d0) < gtol) { p1 = c; done = true; break; }
+            if (!((c.alpha - lo.alpha) * dir > 0.f && (hi.alpha - c.alpha) * dir > 0.f)) continue;
+            if (c.d0 * dir < 0.f) lo = c; else hi = c;
+            moved = true;
+            if (c.cost < best.cost) best = c;
+          }
+          if (done) break;
+          if (!moved) { p1 = best; break; }
+          p1 = lo.cost < hi.cost ? lo : hi;
+        }
+      }
+    }
+    const float alpha = p1.alpha;
+    if (alpha == 0.f) break;
+    for (int k = lane; k < nv; k += 32) { qacc[k] = fmaf(alpha, search[k], qacc[k]); Ma[k] = fmaf(alpha, Mv[k], Ma[k]); }
+    float c2 = 0.f;
+    for (int r = lane; r < nefc; r += 32) {
+      const float jar = EFC(E_JAR, r) + alpha * EFC(E_JV, r);
+      EFC(E_JAR, r) = jar;
+      if (((EFCI(E_DESC0, r) & 3) == ROW_EQ) || jar < 0.f) c2 += 0.5f * EFC(E_D, r) * jar * jar;
+    }
+    __syncwarp();
+    float g = 0.f;
+    for (int k = lane; k < nv; k += 32) g += 0.5f * (Ma[k] - smooth[k]) * (qacc[k] - qas[k]);
+    gauss = warpSum(g);
+    const float newcost = gauss + warpSum(c2);
+    iter++;
+    const float improvement = scale * (cost - newcost);
+    cost = newcost;
+    if (improvement < D.tolerance) {
+      constraintForce(D, L, sm, lane, ncon, nefc, tmp);
+      break;
+    }
+  }
+  // tmp holds J^T f for the final jar in every exit path below except the early sn/alpha breaks: recompute to be safe
+  constraintForce(D, L, sm, lane, ncon, nefc, sm + L.qfrc_con);
+  return iter;
+}
+
+// ------------------------------------------------------------------------------------------ contact / efc outputs
+__device__ void writeConstraintOutputs(const DevModel& D, const SmemLayout& L, const FieldPtrs& F, float* sm, int lane, size_t w, int ncon,
+                                       int nefc, int niter) {
+  const int nv = D.nv, ncm = D.nconmax, njm = D.njmax, nb = D.maxbase;
+  int* ip;
+  if (lane == 0) {
+    if ((ip = (int*)F.p[MYO_F_NCON])) ip[w] = ncon;
+    if ((ip = (int*)F.p[MYO_F_NEFC])) ip[w] = nefc;
+    if ((ip = (int*)F.p[MYO_F_SOLVER_NITER])) ip[w] = niter;
+  }
+  for (int c = lane; c < ncm; c += 32) {
+    const bool on = c < ncon;
+    const float* cr = sm + L.con + 12 * c;
+    const int pr = on ? __float_as_int(cr[7]) : 0;
+    const float* pp = D.pair_prm + 16 * pr;
+    float* o;
+    if ((ip = (int*)F.p[MYO_F_CONTACT_GEOM])) {
+      ip[(w * ncm + c) * 2] = on ? D.cg_geom[D.pair_cg1[pr]] : -1; ip[(w * ncm + c) * 2 + 1] = on ? D.cg_geom[D.pair_cg2[pr]] : -1;
+    }
+    if ((ip = (int*)F.p[MYO_F_CONTACT_DIM])) ip[w * ncm + c] = on ? __float_as_int(cr[9]) : 0;
+    if ((ip = (int*)F.p[MYO_F_CONTACT_EFC_ADDRESS])) ip[w * ncm + c] = on ? __float_as_int(cr[8]) : -1;
+    if ((o = (float*)F.p[MYO_F_CONTACT_DIST])) o[w * ncm + c] = on ? cr[0] : 0.f;
+    if ((o = (float*)F.p[MYO_F_CONTACT_POS])) for (int k = 0; k < 3; k++) o[(w * ncm + c) * 3 + k] = on ? cr[1 + k] : 0.f;
+    if ((o = (float*)F.p[MYO_F_CONTACT_FRAME])) {
+      f3 n = mk3(0.f, 0.f, 0.f), y = n, z = n;
+      if (on) { n = ld3(cr + 4); makeFrame(n, &y, &z); }
+      st3(o + (w * ncm + c) * 9, n); st3(o + (w * ncm + c) * 9 + 3, y); st3(o + (w * ncm + c) * 9 + 6, z);
+    }
+    if ((o = (float*)F.p[MYO_F_CONTACT_INCLUDEMARGIN])) o[w * ncm + c] = on ? pp[0] - pp[1] : 0.f;
+    if ((o = (float*)F.p[MYO_F_CONTACT_FRICTION])) for (int k = 0; k < 5; k++) o[(w * ncm + c) * 5 + k] = on ? pp[2 + k] : 0.f;
+    if ((o = (float*)F.p[MYO_F_CONTACT_SOLREF])) for (int k = 0; k < 2; k++) o[(w * ncm + c) * 2 + k] = on ? pp[7 + k] : 0.f;
+    if ((o = (float*)F.p[MYO_F_CONTACT_SOLIMP])) for (int k = 0; k < 5; k++) o[(w * ncm + c) * 5 + k] = on ? pp[9 + k] : 0.f;
+  }
+  for (int r = lane; r < njm; r += 32) {
+    const bool on = r < nefc;
+    float* o;
+    if ((o = (float*)F.p[MYO_F_EFC_POS])) o[w * njm + r] = on ? EFC(E_POS, r) : 0.f;
+    if ((o = (float*)F.p[MYO_F_EFC_MARGIN])) o[w * njm + r] = on ? EFC(E_MARGIN, r) : 0.f;
+    if ((o = (float*)F.p[MYO_F_EFC_D])) o[w * njm + r] = on ? EFC(E_D, r) : 0.f;
+    if ((o = (float*)F.p[MYO_F_EFC_AREF])) o[w * njm + r] = on ? EFC(E_AREF, r) : 0.f;
+    if ((o = (float*)F.p[MYO_F_EFC_FORCE])) o[w * njm + r] = on ? EFC(E_FORCE, r) : 0.f;
+    if ((ip = (int*)F.p[MYO_F_EFC_TYPE])) {
+      int ty = -1;
+      if (on) {
+        const int t = EFCI(E_DESC0, r) & 3;
+        ty = t == ROW_EQ ? 0 : (t == ROW_LIMJ ? 3 : (t == ROW_LIMT ? 4 : (EFCI(E_DESC1, r) < 0 ? 5 : 6)));
+      }
+      ip[w * njm + r] = ty;
+    }
+  }
+  float* J = (float*)F.p[MYO_F_EFC_J];
+  if (J) {
+    const size_t n = (size_t)njm * nv;
+    for (int i = lane; i < (int)n; i += 32) {
+      const int r = i / nv, k = i - r * nv;
+      float v = 0.f;
+      if (r < nefc) {
+        const int d0 = EFCI(E_DESC0, r), type = d0 & 3, id = d0 >> 2;
+        const float coef = EFC(E_COEF, r);
+        if (type == ROW_LIMJ) v = D.limj_dof[id] == k ? coef : 0.f;
+        else if (type == ROW_EQ) v = D.eq_dof1[id] == k ? 1.f : (D.eq_dof2[id] == k ? coef : 0.f);
+        else if (type == ROW_CON) { const int t = EFCI(E_DESC1, r); v = sm[L.conJ + id * nv + k] + (t >= 0 ? coef * sm[L.conJ + t * nv + k] : 0.f); }
+        else { const int t = D.limt_ten[id]; for (int q = D.ten_nzstart[t]; q < D.ten_nzstart[t + 1]; q++) if (D.nz_dof[q] == k) v = coef * sm[L.tenJ + q]; }
+      }
+      J[w * n + i] = v;
+    }
+  }
+  (void)nb;
+}
+
+__constant__ FieldPtrs kNoFields;  // all NULL: substeps before the last one materialise nothing
+
+__device__ __forceinline__ bool warpAnyBad(const float* v, int n, int lane) {
+  bool bad = false;
+  for (int i = lane; i < n; i += 32) bad |= !(fabsf(v[i]) < 1e10f);
+  return __any_sync(FULLMASK, bad);
+}
+__device__ void resetState(const DevModel& D, const SmemLayout& L, float* sm, int lane) {
+  for (int i = lane; i < D.nq; i += 32) sm[L.qpos + i] = D.qpos0[i];
+  for (int i = lane; i < D.nv; i += 32) { sm[L.qvel + i] = 0.f; sm[L.warm + i] = 0.f; }
+  for (int i = lane; i < D.na; i += 32) sm[L.act + i] = 0.f;
+  __syncwarp();
+}
+
+template <int WARPS>
+__global__ void __launch_bounds__(32 * WARPS) stepKernel(const DevModel D, const SmemLayout L, const FieldPtrs F, int nworld, int nsub,
+                                                         int forward_only, const int* __restrict__ mask, int do_reset) {
+  extern __shared__ float smem[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const size_t w = (size_t)blockIdx.x * WARPS + warp;
+  if (w >= (size_t)nworld) return;
+  if (do_reset && mask && !mask[w]) return;
+  float* sm = smem + (size_t)warp * L.total;
+  const int nq = D.nq, nv = D.nv, na = D.na, nu = D.nu;
+  float* gq = (float*)F.p[MYO_F_QPOS] + w * nq; float* gv = (float*)F.p[MYO_F_QVEL] + w * nv;
+  float* ga = (float*)F.p[MYO_F_ACT] + w * na; const float* gc = (const float*)F.p[MYO_F_CTRL] + w * nu;
+  float* gw = (float*)F.p[MYO_F_QACC_WARMSTART] + w * nv; float* gt = (float*)F.p[MYO_F_TIME] + w;
+  int* gs = (int*)F.p[MYO_F_STATUS];
+  int status = gs ? gs[w] : 0;
+  float time = *gt;
+  if (do_reset) {
+    resetState(D, L, sm, lane);
+    for (int i = lane; i < nu; i += 32) sm[L.ctrl + i] = 0.f;
+    time = 0.f; status = 0;
+  } else {
+    for (int i = lane; i < nq; i += 32) sm[L.qpos + i] = gq[i];
+    for (int i = lane; i < nv; i += 32) { sm[L.qvel + i] = gv[i]; sm[L.warm + i] = gw[i]; }
+    for (int i = lane; i < na; i += 32) sm[L.act + i] = ga[i];
+    for (int i = lane; i < nu; i += 32) sm[L.ctrl + i] = gc[i];
+  }
+  __syncwarp();
+  const int nloop = forward_only ? 1 : nsub;
+  for (int sub = 0; sub < nloop; sub++) {
+    const bool last = sub == nloop - 1;
+    const FieldPtrs& Fo = last ? F : kNoFields;
+    if (!forward_only) {   // mj_checkPos / mj_checkVel
+      if (warpAnyBad(sm + L.qpos, nq, lane)) { resetState(D, L, sm, lane); status |= MYO_WORLD_BADQPOS; }
+      if (warpAnyBad(sm + L.qvel, nv, lane)) { resetState(D, L, sm, lane); status |= MYO_WORLD_BADQVEL; }
+    }
+    int ncon = 0, nefc = 0, niter = 0;
+    for (int attempt = 0; attempt < 2; attempt++) {
+      kinematics(D, L, sm, lane);
+      comPos(D, L, sm, lane);
+      if (last) writePositionOutputs(D, L, Fo, sm, lane, w);
+      tendons(D, L, Fo, sm, lane, w);
+      inertia(D, L, Fo, sm, lane, w);
+      __syncwarp();
+      ncon = (D.disableflags & (DSBL_CONTACT | DSBL_CONSTRAINT)) ? 0 : collision(D, L, sm, lane, &status);
+      velocity(D, L, Fo, sm, lane, w);
+      actuation(D, L, Fo, sm, lane, w);
+      __syncwarp();
+      nefc = makeConstraint(D, L, sm, lane, ncon, &status);
+      niter = 0;
+      if (nefc == 0) {
+        for (int i = lane; i < nv; i += 32) { const float a = sm[L.qacc_smooth + i]; sm[L.qacc + i] = a; sm[L.warm + i] = a; sm[L.qfrc_con + i] = 0.f; }
+      } else {
+        niter = solveNewton(D, L, sm, lane, ncon, nefc, &status);
+        for (int i = lane; i < nv; i += 32) sm[L.warm + i] = sm[L.qacc + i];
+      }
+      __syncwarp();
+      if (forward_only || !warpAnyBad(sm + L.qacc, nv, lane)) break;
+      resetState(D, L, sm, lane);   // mj_checkAcc: reset and redo the forward pass
+      status |= MYO_WORLD_BADQACC;
+    }
+    if (last) {
+      writeConstraintOutputs(D, L, Fo, sm, lane, w, ncon, nefc, niter);
+      float* o;
+      if ((o = (float*)F.p[MYO_F_QACC])) for (int i = lane; i < nv; i += 32) o[w * nv + i] = sm[L.qacc + i];
+      if ((o = (float*)F.p[MYO_F_QFRC_CONSTRAINT])) for (int i = lane; i < nv; i += 32) o[w * nv + i] = sm[L.qfrc_con + i];
+      if ((o = (float*)F.p[MYO_F_QFRC_INVERSE])) for (int i = lane; i < nv; i += 32) o[w * nv + i] = 0.f;
+    }
+    if (forward_only) break;
+    // ---- mj_Euler with implicit joint damping
+    const float h = D.timestep;
+    float* qa = sm + L.tmpv;
+    if (D.any_damping) {
+      for (int e = lane; e < D.nM; e += 32) sm[L.qH + e] = sm[L.qM + e] + (D.M_row[e] == D.M_col[e] ? h * D.dof_damping[D.M_row[e]] : 0.f);
+      for (int i = lane; i < nv; i += 32) qa[i] = sm[L.smooth + i] + sm[L.qfrc_con + i];
+      __syncwarp();
+      factorLDL(D, sm + L.qH, sm + L.qHinv, lane);
+      solveLDL(D, sm + L.qH, sm + L.qHinv, qa, lane);
+    } else {
+      for (int i = lane; i < nv; i += 32) qa[i] = sm[L.qacc + i];
+      __syncwarp();
+    }
+    if (!(D.disableflags & DSBL_ACTUATION))
+      for (int i = lane; i < nu; i += 32) {
+        const int aa = D.act_actadr[i];
+        if (aa < 0) continue;
+        float a = fmaf(h, sm[L.actdot + aa], sm[L.act + aa]);
+        if (D.act_flags[i] & ACT_ACTLIMITED) a = clipf(a, D.act_actrange[2 * i], D.act_actrange[2 * i + 1]);
+        sm[L.act + aa] = a;
+      }
+    for (int i = lane; i < nv; i += 32) sm[L.qvel + i] = fmaf(h, qa[i], sm[L.qvel + i]);
+    __syncwarp();
+    for (int j = lane; j < D.njnt; j += 32) {
+      const int qa_ = D.jnt_qposadr[j], da = D.jnt_dofadr[j];
+      if (D.jnt_type[j] == JNT_FREE) {
+        for (int k = 0; k < 3; k++) sm[L.qpos + qa_ + k] = fmaf(h, sm[L.qvel + da + k], sm[L.qpos + qa_ + k]);
+        const f3 wv = ld3(sm + L.qvel + da + 3);
+        const float ang = norm3(wv) * h;
+        if (ang > 0.f) {
+          const f3 ax = unit3(wv);
+          float sn, cs; sincosf(0.5f * ang, &sn, &cs);
+          f4 dq; dq.w = cs; dq.x = ax.x * sn; dq.y = ax.y * sn; dq.z = ax.z * sn;
+          st4(sm + L.qpos + qa_ + 3, qnormalize(qmul(ld4(sm + L.qpos + qa_ + 3), dq)));
+        }
+      } else sm[L.qpos + qa_] = fmaf(h, sm[L.qvel + da], sm[L.qpos + qa_]);
+    }
+    time += h;
+    __syncwarp();
+  }
+  // ---- state out
+  if (!forward_only || do_reset) {
+    for (int i = lane; i < nq; i += 32) gq[i] = sm[L.qpos + i];
+    for (int i = lane; i < nv; i += 32) gv[i] = sm[L.qvel + i];
+    for (int i = lane; i < na; i += 32) ga[i] = sm[L.act + i];
+    if (lane == 0) *gt = time;
+  }
+  for (int i = lane; i < nv; i += 32) gw[i] = sm[L.warm + i];
+  if (gs && lane == 0) gs[w] = status;
+}
+
+int64_t g_launches = 0;
+
+}  // namespace
+
+int myo_kernel_smem_bytes(const SmemLayout& L) { return L.total * (int)sizeof(float); }
+int64_t myo_launch_counter() { return g_launches; }
+
+int myo_launch_step(const DevModel& D, const SmemLayout& L, const FieldPtrs& F, int nworld, int nsub, int forward_only,
+                    const int* reset_mask, int do_reset, void* stream) {
+  constexpr int WARPS = 1;
+  const size_t smem = (size_t)WARPS * L.total * sizeof(float);
+  static size_t configured = 0;
+  if (smem > configured) {
+    if (cudaFuncSetAttribute(stepKernel<WARPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return -1;
+    configured = smem;
+  }
+  const int grid = (nworld + WARPS - 1) / WARPS;
+  stepKernel<WARPS><<<grid, 32 * WARPS, smem, (cudaStream_t)stream>>>(D, L, F, nworld, nsub, forward_only, reset_mask, do_reset);
+  g_launches++;
+  return cudaPeekAtLastError() == cudaSuccess ? 0 : -1;
+}

@@ -1,0 +1,199 @@
+"""MJX-shaped host API over libmyostep.so.
+
+Mirrors what the reference calls on `mujoco.mjx` (third-party; call sites myosuite/mjx/play.py:10-11,41,47,49):
+
+    model = mjx.put_model(mj_model)            ->  put_model(mj_model)
+    data  = mjx.put_data(mj_model, mj_data)    ->  put_data(model, mj_data, nworld=...)
+    data  = jax.jit(mjx.step)(model, data)     ->  step(model, data)          (vmapped: leading world axis)
+    mj_d  = mjx.get_data(mj_model, data)       ->  get_data(model, data)
+
+Field names are mjData's; every `Data` attribute is a torch CUDA tensor `[nworld, ...]` that the kernel reads and
+writes in place (zero-copy: the tensors' storage is bound to the batch through `myo_batch_bind`; any DLPack
+producer can be bound the same way, see `Data.bind`).  `step` returns the same `Data` object; call
+`data.clone()` first if the functional, non-aliasing behaviour of `mjx.step` is needed.
+Unsupported model features raise `NotImplementedError` at `put_model`, as MJX does.  No CPU fallback exists.
+"""
+from __future__ import annotations
+
+import ctypes
+from types import SimpleNamespace
+
+import numpy as np
+import torch
+
+from . import desc as _desc
+from . import lib as _lib
+from . import mjcf as _mjcf
+
+STATE_FIELDS = ("qpos", "qvel", "act", "ctrl", "time", "qacc_warmstart", "status")
+# the subset a policy loop needs ("mode B" in DESIGN.md)
+CORE_FIELDS = STATE_FIELDS + ("qacc", "actuator_force", "actuator_length", "actuator_velocity")
+
+_SHAPES = {
+    "xpos": ("nbody", 3), "xquat": ("nbody", 4), "xmat": ("nbody", 9), "xipos": ("nbody", 3), "ximat": ("nbody", 9),
+    "xanchor": ("njnt", 3), "xaxis": ("njnt", 3), "geom_xpos": ("ngeom", 3), "geom_xmat": ("ngeom", 9),
+    "site_xpos": ("nsite", 3), "site_xmat": ("nsite", 9), "subtree_com": ("nbody", 3), "cinert": ("nbody", 10),
+    "crb": ("nbody", 10), "cdof": ("nv", 6), "cdof_dot": ("nv", 6), "cvel": ("nbody", 6), "ten_j": ("ntendon", "nv"),
+    "actuator_moment": ("nu", "nv"), "qm": ("nv", "nv"), "qld": ("nv", "nv"), "contact_geom": (-1, 2), "contact_pos": (-1, 3),
+    "contact_frame": (-1, 9), "contact_friction": (-1, 5), "contact_solref": (-1, 2), "contact_solimp": (-1, 5),
+    "efc_j": (-1, "nv"),
+}
+
+
+class Model:
+    """Device-resident compiled model (mjx.Model counterpart).  `.mj` is the host mjModel-shaped object."""
+
+    def __init__(self, mj, device=0):
+        self.mj = mj
+        self.device = int(device)
+        self._desc, self._keep = _desc.pack(mj)
+        h = ctypes.c_void_p()
+        rc = _lib.lib().myo_model_create(ctypes.byref(self._desc), self.device, ctypes.byref(h))
+        if rc == -2:
+            raise NotImplementedError(_lib.lib().myo_last_error().decode())
+        _lib.check(rc)
+        self._h = h
+        for k in ("nq", "nv", "nu", "na", "nbody", "njnt", "ngeom", "nsite", "ntendon"):
+            setattr(self, k, int(getattr(mj, k)))
+
+    def __del__(self):
+        try:
+            _lib.lib().myo_model_destroy(self._h)
+        except Exception:
+            pass
+
+
+class Data:
+    """A batch of `nworld` worlds (vmapped mjx.Data counterpart).  Attributes are torch tensors `[nworld, ...]`."""
+
+    def __init__(self, model, nworld, fields="all", nconmax=0, njmax=0):
+        L = _lib.lib()
+        self.model = model
+        self.nworld = int(nworld)
+        h = ctypes.c_void_p()
+        _lib.check(L.myo_batch_create(model._h, self.nworld, int(nconmax), int(njmax), ctypes.byref(h)))
+        self._h = h
+        self.nconmax = L.myo_batch_nconmax(h)
+        self.njmax = L.myo_batch_njmax(h)
+        self._t = {}
+        dev = torch.device("cuda", model.device)
+        if fields == "all":
+            names = [n.lower() for n in _desc.FIELD_NAMES]
+        elif fields == "core":
+            names = list(CORE_FIELDS)
+        else:
+            names = list(dict.fromkeys(list(STATE_FIELDS) + list(fields)))
+        for name in names:
+            fid = _desc.FIELD_ID[name]
+            cnt = L.myo_field_count(h, fid)
+            if cnt == 0:
+                continue
+            dt = torch.int32 if L.myo_field_is_int(fid) else torch.float32
+            self.bind(name, torch.zeros((self.nworld, cnt), dtype=dt, device=dev))
+
+    # -- zero-copy binding of caller-owned device memory (torch tensor or anything exporting __dlpack__)
+    def bind(self, name, tensor):
+        if not isinstance(tensor, torch.Tensor):
+            tensor = torch.from_dlpack(tensor)
+        if not tensor.is_cuda or not tensor.is_contiguous():
+            raise ValueError("bound buffers must be contiguous CUDA tensors")
+        fid = _desc.FIELD_ID[name.lower()]
+        _lib.check(_lib.lib().myo_batch_bind(self._h, fid, ctypes.c_void_p(tensor.data_ptr()), tensor.numel() * tensor.element_size()))
+        self._t[name.lower()] = tensor
+
+    def __getattr__(self, name):
+        t = self.__dict__.get("_t", {})
+        key = name.lower()
+        if key in t:
+            return self._view(key, t[key])
+        raise AttributeError(name)
+
+    def _view(self, key, t):
+        shp = _SHAPES.get(key)
+        if shp is None:
+            return t
+        mj = self.model.mj
+        dims = [d if isinstance(d, int) else int(getattr(mj, d)) for d in shp]
+        return t.view(self.nworld, *dims)
+
+    def fields(self):
+        return list(self._t)
+
+    def clone(self):
+        d = Data.__new__(Data)
+        L = _lib.lib()
+        d.model, d.nworld = self.model, self.nworld
+        h = ctypes.c_void_p()
+        _lib.check(L.myo_batch_create(self.model._h, self.nworld, self.nconmax, self.njmax, ctypes.byref(h)))
+        d._h, d.nconmax, d.njmax, d._t = h, self.nconmax, self.njmax, {}
+        for k, v in self._t.items():
+            d.bind(k, v.clone())
+        return d
+
+    def __del__(self):
+        try:
+            _lib.lib().myo_batch_destroy(self._h)
+        except Exception:
+            pass
+
+
+def _stream():
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def put_model(mj_model, device=0) -> Model:
+    """mjx.put_model (reference: myosuite/mjx/play.py:10).  `mj_model`: mjcf.Model, a path to an MJCF file, or a
+    real mujoco.MjModel."""
+    if isinstance(mj_model, str):
+        mj_model = _mjcf.from_xml_path(mj_model)
+    return Model(mj_model, device)
+
+
+def make_data(model, nworld=1, fields="all", nconmax=0, njmax=0) -> Data:
+    d = Data(model, nworld, fields, nconmax, njmax)
+    d.qpos[:] = torch.as_tensor(np.asarray(model.mj.qpos0), dtype=torch.float32, device=d.qpos.device)
+    return d
+
+
+def put_data(model, mj_data=None, nworld=1, fields="all", nconmax=0, njmax=0) -> Data:
+    """mjx.put_data (reference: myosuite/mjx/play.py:11): host state (qpos, qvel, act, ctrl, time, qacc_warmstart;
+    each `[n]` or `[nworld, n]`) -> device batch."""
+    d = make_data(model, nworld, fields, nconmax, njmax)
+    if mj_data is not None:
+        for name in ("qpos", "qvel", "act", "ctrl", "qacc_warmstart", "time"):
+            v = getattr(mj_data, name, None) if not isinstance(mj_data, dict) else mj_data.get(name)
+            if v is None:
+                continue
+            t = torch.as_tensor(np.asarray(v, dtype=np.float32)).reshape(-1 if np.ndim(v) < 2 else (np.shape(v)[0], -1))
+            getattr(d, name)[:] = t.to(d.qpos.device)
+    return d
+
+
+def forward(model, data) -> Data:
+    """mjx.forward / mj_forward (reference: sim.forward(), myosuite/robot/robot.py:979)."""
+    _lib.check(_lib.lib().myo_forward(data._h, _stream()))
+    return data
+
+
+def step(model, data, nsubsteps=1) -> Data:
+    """mjx.step (reference: myosuite/mjx/play.py:47); `nsubsteps` fuses n mj_steps with ctrl held
+    (reference: sim.advance(substeps=n_frames), myosuite/robot/robot.py:880-882)."""
+    _lib.check(_lib.lib().myo_step(data._h, int(nsubsteps), _stream()))
+    return data
+
+
+def reset(model, data, mask=None) -> Data:
+    """mj_resetData + mj_forward on the masked worlds (reference: myosuite/robot/robot.py:976-979)."""
+    if mask is not None:
+        mask = mask.to(device=data.qpos.device, dtype=torch.int32).contiguous()
+    _lib.check(_lib.lib().myo_reset(data._h, ctypes.c_void_p(mask.data_ptr()) if mask is not None else None, _stream()))
+    return data
+
+
+def get_data(model, data):
+    """mjx.get_data (reference: myosuite/mjx/play.py:49): device batch -> host numpy arrays (one namespace,
+    leading world axis kept)."""
+    out = SimpleNamespace()
+    for k in data.fields():
+        setattr(out, k, getattr(data, k).detach().cpu().numpy())
+    return out
