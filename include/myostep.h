@@ -182,6 +182,7 @@ int myo_batch_create(const myo_model *m, int nworld, int nconmax, int njmax, myo
 void myo_batch_destroy(myo_batch *b);
 int myo_batch_nconmax(const myo_batch *b);
 int myo_batch_njmax(const myo_batch *b);
+int myo_batch_smem_bytes(const myo_batch *b);   /* shared-memory arena per world (one warp) */
 
 /* Per-world element count / element size of a field for this batch (0 elements = field absent for the model). */
 int64_t myo_field_count(const myo_batch *b, int field);

@@ -371,24 +371,28 @@ __device__ float wrapInside(float* pnt, const float* d, float rad) {
   if (cosG < -1.f + 1e-7f) return -1.f;
   if (cosG > 1.f - 1e-7f) return 0.f;
   const float G = acosf(cosG);
-  float z = 1.f - 1e-6f;
-  float f = asinf(A * z) + asinf(B * z) - 2.f * asinf(z) + G;
+  // Root of asin(A z) + asin(B z) - 2 asin(z) + G on z in (0,1).  MuJoCo iterates on z from z = 1 - 1e-7, where
+  // d/dz blows up and float32 cannot resolve the root; we iterate on t = acos(z) instead (same function, same
+  // root, same bail-out tests translated: df/dz > 0 <=> dg/dt < 0, z increasing <=> t decreasing).
+  float t = 4.4721e-4f;  // acos(1 - 1e-7)
+  float ct = cosf(t);
+  float f = asinf(A * ct) + asinf(B * ct) + 2.f * t - CUDART_PI_F + G;
   if (f > 0.f) return 0.f;
   int it = 0;
   for (; it < 20 && fabsf(f) > 1e-6f; it++) {
-    const float df = A / fmaxf(MINVAL, sqrtf(1.f - z * z * A * A)) + B / fmaxf(MINVAL, sqrtf(1.f - z * z * B * B)) -
-                     2.f / fmaxf(MINVAL, sqrtf(1.f - z * z));
-    if (df > -MINVAL) return 0.f;
-    const float z1 = z - f / df;
-    if (z1 > z) return 0.f;
-    z = z1;
-    f = asinf(A * z) + asinf(B * z) - 2.f * asinf(z) + G;
-    if (f > 1e-6f) return 0.f;
+    const float st = sinf(t);
+    const float dg = 2.f - st * (A / fmaxf(1e-12f, sqrtf(1.f - ct * ct * A * A)) + B / fmaxf(1e-12f, sqrtf(1.f - ct * ct * B * B)));
+    if (dg < 1e-12f) return 0.f;
+    const float t1 = t - f / dg;
+    if (t1 < t) return 0.f;
+    t = t1; ct = cosf(t);
+    f = asinf(A * ct) + asinf(B * ct) + 2.f * t - CUDART_PI_F + G;
+    if (f > 1e-5f) return 0.f;
   }
   if (it >= 20) return 0.f;
   float vx, vy, ang;
-  if (d[0] * d[3] - d[1] * d[2] > 0.f) { vx = d[0] / l0; vy = d[1] / l0; ang = asinf(z) - asinf(A * z); }
-  else { vx = d[2] / l1; vy = d[3] / l1; ang = asinf(z) - asinf(B * z); }
+  if (d[0] * d[3] - d[1] * d[2] > 0.f) { vx = d[0] / l0; vy = d[1] / l0; ang = 0.5f * CUDART_PI_F - t - asinf(A * ct); }
+  else { vx = d[2] / l1; vy = d[3] / l1; ang = 0.5f * CUDART_PI_F - t - asinf(B * ct); }
   float sn, cs; sincosf(ang, &sn, &cs);
   pnt[0] = pnt[2] = rad * (cs * vx - sn * vy);
   pnt[1] = pnt[3] = rad * (sn * vx + cs * vy);

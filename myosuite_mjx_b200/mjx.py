@@ -75,6 +75,7 @@ class Data:
         self._h = h
         self.nconmax = L.myo_batch_nconmax(h)
         self.njmax = L.myo_batch_njmax(h)
+        self.smem_bytes = L.myo_batch_smem_bytes(h)
         self._t = {}
         dev = torch.device("cuda", model.device)
         if fields == "all":

@@ -1407,7 +1407,8 @@ void* orc_field(void* hv, const char* name, int64_t* count, int* is_int) {
   auto it = f.find(name);
   if (it == f.end()) return nullptr;
   *count = it->second.second.first; *is_int = it->second.second.second;
-  return it->second.first;
+  static double dummy[2];
+  return it->second.first ? it->second.first : (void*)dummy;
 }
 int orc_scalar_size(void* hv) { return ((Handle*)hv)->is_float ? 4 : 8; }
 
