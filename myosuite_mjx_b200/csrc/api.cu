@@ -24,11 +24,15 @@ struct myo_batch {
   SmemLayout L;
   FieldPtrs F;
   int nworld;
+  int slot;      // constant-memory parameter slot
+  int warps;     // worlds per CTA
+  bool dirty;    // parameters changed since the last upload
   std::vector<void*> owned;
 };
 
 namespace {
 thread_local std::string g_err;
+bool g_slot_used[64] = {false};
 int fail(int code, const std::string& msg) { g_err = msg; return code; }
 
 const char* kFieldNames[MYO_F_COUNT] = {
@@ -133,12 +137,15 @@ int myo_batch_create(const myo_model* m, int nworld, int nconmax, int njmax, myo
   if (!m || !out || nworld <= 0) return fail(MYO_ERR_ARG, "bad argument");
   if (cudaSetDevice(m->device) != cudaSuccess) return fail(MYO_ERR_CUDA, "cudaSetDevice failed");
   myo_batch* b = new myo_batch();
-  b->model = m; b->D = m->D; b->nworld = nworld;
+  b->model = m; b->D = m->D; b->nworld = nworld; b->slot = -1; b->dirty = true;
+  for (int i = 0; i < myo_param_slots(); i++) if (!g_slot_used[i]) { b->slot = i; g_slot_used[i] = true; break; }
+  if (b->slot < 0) { delete b; return fail(MYO_ERR_ARG, "too many live batches (8 constant-memory parameter slots)"); }
   memset(&b->F, 0, sizeof(b->F));
   try {
     myo_make_layout(b->D, nconmax, njmax, b->L);
-  } catch (const std::string& e) { delete b; return fail(MYO_ERR_ARG, e); }
-  if (myo_kernel_smem_bytes(b->L) > 220 * 1024) { delete b; return fail(MYO_ERR_UNSUPPORTED, "model does not fit the per-world shared-memory arena"); }
+  } catch (const std::string& e) { g_slot_used[b->slot] = false; delete b; return fail(MYO_ERR_ARG, e); }
+  b->warps = myo_pick_warps(b->L);
+  if (myo_kernel_smem_bytes(b->L) > 220 * 1024) { g_slot_used[b->slot] = false; delete b; return fail(MYO_ERR_UNSUPPORTED, "model does not fit the per-world shared-memory arena"); }
   // library-owned default state buffers (bind overrides them)
   for (int f : kStateFields) {
     void* p = nullptr;
@@ -153,6 +160,7 @@ void myo_batch_destroy(myo_batch* b) {
   if (!b) return;
   cudaSetDevice(b->model->device);
   for (void* p : b->owned) cudaFree(p);
+  if (b->slot >= 0) g_slot_used[b->slot] = false;
   delete b;
 }
 int myo_batch_nconmax(const myo_batch* b) { return b ? b->D.nconmax : 0; }
@@ -171,13 +179,18 @@ int myo_batch_bind(myo_batch* b, int field, void* dev_ptr, int64_t nbytes) {
     for (int f : kStateFields) if (f == field) return fail(MYO_ERR_ARG, "state fields cannot be unbound");
   }
   b->F.p[field] = dev_ptr;
+  b->dirty = true;
   return MYO_OK;
 }
 
 static int launch(myo_batch* b, int nsub, int forward_only, const int32_t* mask, int do_reset, void* stream) {
   int rc = checkReady(b);
   if (rc) return rc;
-  if (myo_launch_step(b->D, b->L, b->F, b->nworld, nsub, forward_only, mask, do_reset, stream) != 0)
+  if (b->dirty) {
+    if (myo_upload_params(b->slot, b->D, b->L, b->F, stream) != 0) return fail(MYO_ERR_CUDA, "parameter upload failed");
+    b->dirty = false;
+  }
+  if (myo_launch_step(b->slot, b->L, b->nworld, nsub, forward_only, mask, do_reset, b->warps, stream) != 0)
     return fail(MYO_ERR_CUDA, std::string("kernel launch failed: ") + cudaGetErrorString(cudaGetLastError()));
   return MYO_OK;
 }

@@ -15,6 +15,11 @@
 #define MINVAL 1e-15f
 #define FULLMASK 0xffffffffu
 
+struct Params { DevModel D; SmemLayout L; FieldPtrs F; };
+#define MYO_NSLOT 8
+// per-batch kernel parameters live in constant memory (slot MYO_NSLOT is all zero: "materialise nothing")
+__constant__ Params cP[MYO_NSLOT + 1];
+
 namespace {
 
 enum { JNT_FREE = 0, JNT_BALL = 1, JNT_SLIDE = 2, JNT_HINGE = 3 };
@@ -95,13 +100,23 @@ __device__ __forceinline__ void crossForce(float* r, const float* vel, const flo
   st3(r, cross(w, a) + cross(l, b)); st3(r + 3, cross(w, b));
 }
 
+
+// one out-of-line copy of each heavy libm routine (their inlined slow paths were most of the kernel's code size)
+__device__ __noinline__ void sincos_(float x, float* s, float* c) { sincosf(x, s, c); }
+__device__ __noinline__ float asin_(float x) { return asinf(x); }
+__device__ __noinline__ float acos_(float x) { return acosf(x); }
+__device__ __noinline__ float pow_(float x, float y) { return powf(x, y); }
+__device__ __noinline__ float cos_(float x) { return cosf(x); }
+__device__ __noinline__ float sin_(float x) { return sinf(x); }
+
 // frame record in shared memory: pos[3], quat[4], mat[9]
 #define FR_POS(sm, L, f) ((sm) + (L).frames + 16 * (f))
 #define FR_QUAT(sm, L, f) ((sm) + (L).frames + 16 * (f) + 3)
 #define FR_MAT(sm, L, f) ((sm) + (L).frames + 16 * (f) + 7)
 
 // ------------------------------------------------------------------------------------------ kinematics
-__device__ void kinematics(const DevModel& D, const SmemLayout& L, float* sm, int lane) {
+__device__ __noinline__ void kinematics(int slot, float* sm, int lane) {
+  const DevModel& D = cP[slot].D; const SmemLayout& L = cP[slot].L;
   if (lane == 0) {
     float* p = FR_POS(sm, L, 0);
     p[0] = p[1] = p[2] = 0.f; p[3] = 1.f; p[4] = p[5] = p[6] = 0.f;
@@ -109,7 +124,9 @@ __device__ void kinematics(const DevModel& D, const SmemLayout& L, float* sm, in
   }
   __syncwarp();
   float* qpos = sm + L.qpos;
+  #pragma unroll 1
   for (int l = 0; l < D.nlevel; l++) {
+    #pragma unroll 1
     for (int idx = D.lvl_start[l] + lane; idx < D.lvl_start[l + 1]; idx += 32) {
       const int f = D.lvl_frames[idx], p = D.fr_parent[f], ja = D.fr_jntadr[f], jn = D.fr_jntnum[f];
       f3 pos; f4 quat; float R[9];
@@ -123,6 +140,7 @@ __device__ void kinematics(const DevModel& D, const SmemLayout& L, float* sm, in
         pos = ld3(FR_POS(sm, L, p)) + mulM(FR_MAT(sm, L, p), ld3(D.fr_pre_pos + 3 * f));
         quat = qmul(ld4(FR_QUAT(sm, L, p)), ld4(D.fr_pre_quat + 4 * f));
         q2m(R, quat);
+        #pragma unroll 1
         for (int j = ja; j < ja + jn; j++) {
           const f3 lpos = ld3(D.jnt_pos + 3 * j), laxis = ld3(D.jnt_axis + 3 * j);
           const f3 anchor = mulM(R, lpos) + pos, axis = mulM(R, laxis);
@@ -131,7 +149,7 @@ __device__ void kinematics(const DevModel& D, const SmemLayout& L, float* sm, in
           const float d = qpos[qa] - D.qpos0[qa];
           if (D.jnt_type[j] == JNT_SLIDE) pos = pos + axis * d;
           else {
-            float sn, cs; sincosf(0.5f * d, &sn, &cs);
+            float sn, cs; sincos_(0.5f * d, &sn, &cs);
             f4 ql; ql.w = cs; ql.x = laxis.x * sn; ql.y = laxis.y * sn; ql.z = laxis.z * sn;
             quat = qmul(quat, ql);
             q2m(R, quat);
@@ -151,21 +169,26 @@ __device__ void kinematics(const DevModel& D, const SmemLayout& L, float* sm, in
 }
 
 // composite inertia of every frame about its tree's centre of mass, motion axes (mj_comPos over weld groups)
-__device__ void comPos(const DevModel& D, const SmemLayout& L, float* sm, int lane) {
+__device__ __noinline__ void comPos(int slot, float* sm, int lane) {
+  const DevModel& D = cP[slot].D; const SmemLayout& L = cP[slot].L;
   float* cin = sm + L.cinert;
+  #pragma unroll 1
   for (int f = lane; f < D.nframe; f += 32) {
     f3 cw = ld3(FR_POS(sm, L, f)) + mulM(FR_MAT(sm, L, f), ld3(D.fr_com + 3 * f));
     st3(cin + 10 * f + 6, cw); cin[10 * f + 9] = D.fr_mass[f];
   }
   __syncwarp();
+  #pragma unroll 1
   for (int r = lane; r < D.nroot; r += 32) {
     f3 acc = ld3(D.root_const + 4 * r);
     const float M = D.root_const[4 * r + 3];
+    #pragma unroll 1
     for (int f = D.root_fstart[r]; f < D.root_fend[r]; f++) acc = acc + ld3(cin + 10 * f + 6) * cin[10 * f + 9];
     if (M < MINVAL) acc = mk3(0.f, 0.f, 0.f); else acc = acc * (1.f / M);
     st3(sm + L.rootcom + 3 * r, acc);
   }
   __syncwarp();
+  #pragma unroll 1
   for (int f = lane; f < D.nframe; f += 32) {
     float* c = cin + 10 * f;
     if (f == 0) { for (int k = 0; k < 10; k++) c[k] = 0.f; continue; }
@@ -188,6 +211,7 @@ __device__ void comPos(const DevModel& D, const SmemLayout& L, float* sm, int la
     c[2] = zz + m * (off.x * off.x + off.y * off.y); c[3] = xy - m * off.x * off.y; c[4] = xz - m * off.x * off.z;
     c[5] = yz - m * off.y * off.z; c[6] = m * off.x; c[7] = m * off.y; c[8] = m * off.z;
   }
+  #pragma unroll 1
   for (int j = lane; j < D.njnt; j += 32) {
     const int f = D.jnt_frame[j], da = D.jnt_dofadr[j];
     const f3 off = ld3(sm + L.rootcom + 3 * D.fr_root[f]) - ld3(sm + L.xanchor + 3 * j);
@@ -213,11 +237,13 @@ __device__ void comPos(const DevModel& D, const SmemLayout& L, float* sm, int la
 
 // ------------------------------------------------------------------------------------------ mjData position outputs
 // Written straight to global memory (world-major rows); nothing here feeds the dynamics.
-__device__ void writePositionOutputs(const DevModel& D, const SmemLayout& L, const FieldPtrs& F, float* sm, int lane, size_t w) {
+__device__ __noinline__ void writePositionOutputs(int slot, int fslot, float* sm, int lane, size_t w) {
+  const DevModel& D = cP[slot].D; const SmemLayout& L = cP[slot].L; const FieldPtrs& F = cP[fslot].F;
   float* xpos = (float*)F.p[MYO_F_XPOS]; float* xquat = (float*)F.p[MYO_F_XQUAT]; float* xmat = (float*)F.p[MYO_F_XMAT];
   float* xipos = (float*)F.p[MYO_F_XIPOS]; float* ximat = (float*)F.p[MYO_F_XIMAT]; float* cinert = (float*)F.p[MYO_F_CINERT];
   const int nb = D.nbody;
   if (xpos || xquat || xmat || xipos || ximat || cinert) {
+    #pragma unroll 1
     for (int b = lane; b < nb; b += 32) {
       const int f = D.body_frame[b];
       const float* R = FR_MAT(sm, L, f);
@@ -254,10 +280,12 @@ __device__ void writePositionOutputs(const DevModel& D, const SmemLayout& L, con
   float* crb = (float*)F.p[MYO_F_CRB];
   if ((scom && xipos) || (crb && cinert)) {
     __syncwarp();  // the loops below read back what other lanes of this warp just wrote (L2 loads, ld.global.cg)
+    #pragma unroll 1
     for (int b = lane; b < nb; b += 32) {
       const int e = D.body_subend[b];
       if (scom && xipos) {
         f3 acc = mk3(0.f, 0.f, 0.f);
+        #pragma unroll 1
         for (int c = b; c < e; c++) {
           const float* xp = xipos + (w * nb + c) * 3;
           acc = acc + mk3(__ldcg(xp), __ldcg(xp + 1), __ldcg(xp + 2)) * D.body_mass[c];
@@ -283,6 +311,7 @@ __device__ void writePositionOutputs(const DevModel& D, const SmemLayout& L, con
   float* gp = (float*)F.p[MYO_F_GEOM_XPOS]; float* gm = (float*)F.p[MYO_F_GEOM_XMAT];
   if (gp || gm) {
     const int ng = D.ngeom;
+    #pragma unroll 1
     for (int g = lane; g < ng; g += 32) {
       const int f = D.geom_frame[g];
       if (gp) st3(gp + (w * ng + g) * 3, ld3(FR_POS(sm, L, f)) + mulM(FR_MAT(sm, L, f), ld3(D.geom_lpos + 3 * g)));
@@ -295,6 +324,7 @@ __device__ void writePositionOutputs(const DevModel& D, const SmemLayout& L, con
   float* sp = (float*)F.p[MYO_F_SITE_XPOS]; float* smt = (float*)F.p[MYO_F_SITE_XMAT];
   if (sp || smt) {
     const int ns = D.nsite;
+    #pragma unroll 1
     for (int s = lane; s < ns; s += 32) {
       const int f = D.site_frame[s];
       if (sp) st3(sp + (w * ns + s) * 3, ld3(FR_POS(sm, L, f)) + mulM(FR_MAT(sm, L, f), ld3(D.site_lpos + 3 * s)));
@@ -314,7 +344,7 @@ __device__ __forceinline__ bool segIntersect(const float* p1, const float* p2, c
   const float b = ((p2[0] - p1[0]) * (p1[1] - p3[1]) - (p2[1] - p1[1]) * (p1[0] - p3[0])) / det;
   return a >= 0.f && a <= 1.f && b >= 0.f && b <= 1.f;
 }
-__device__ float wrapCircle(float* pnt, const float* d, const float* sd, float rad) {
+__device__ __noinline__ float wrapCircle(float* pnt, const float* d, const float* sd, float rad) {
   const float sq0 = d[0] * d[0] + d[1] * d[1], sq1 = d[2] * d[2] + d[3] * d[3], sqr = rad * rad;
   const float dx = d[2] - d[0], dy = d[3] - d[1];
   const float dd = dx * dx + dy * dy;
@@ -346,12 +376,12 @@ __device__ float wrapCircle(float* pnt, const float* d, const float* sd, float r
   for (int k = 0; k < 4; k++) pnt[k] = i == 0 ? sol[0][k] : sol[1][k];
   if (segIntersect(d, pnt, d + 2, pnt + 2)) return -1.f;
   const float n0 = fmaxf(MINVAL, sqrtf(pnt[0] * pnt[0] + pnt[1] * pnt[1])), n1 = fmaxf(MINVAL, sqrtf(pnt[2] * pnt[2] + pnt[3] * pnt[3]));
-  float ang = acosf(clipf((pnt[0] * pnt[2] + pnt[1] * pnt[3]) / (n0 * n1), -1.f, 1.f));
+  float ang = acos_(clipf((pnt[0] * pnt[2] + pnt[1] * pnt[3]) / (n0 * n1), -1.f, 1.f));
   const float cr = pnt[1] * pnt[2] - pnt[0] * pnt[3];
   if ((cr > 0.f && i) || (cr < 0.f && !i)) ang = 2.f * CUDART_PI_F - ang;
   return rad * ang;
 }
-__device__ float wrapInside(float* pnt, const float* d, float rad) {
+__device__ __noinline__ float wrapInside(float* pnt, const float* d, float rad) {
   const float l0 = sqrtf(d[0] * d[0] + d[1] * d[1]), l1 = sqrtf(d[2] * d[2] + d[3] * d[3]);
   if (l0 <= rad || l1 <= rad) return -1.f;
   const float dx = d[2] - d[0], dy = d[3] - d[1];
@@ -370,36 +400,37 @@ __device__ float wrapInside(float* pnt, const float* d, float rad) {
   const float cosG = (l0 * l0 + l1 * l1 - dd) / (2.f * l0 * l1);
   if (cosG < -1.f + 1e-7f) return -1.f;
   if (cosG > 1.f - 1e-7f) return 0.f;
-  const float G = acosf(cosG);
+  const float G = acos_(cosG);
   // Root of asin(A z) + asin(B z) - 2 asin(z) + G on z in (0,1).  MuJoCo iterates on z from z = 1 - 1e-7, where
   // d/dz blows up and float32 cannot resolve the root; we iterate on t = acos(z) instead (same function, same
   // root, same bail-out tests translated: df/dz > 0 <=> dg/dt < 0, z increasing <=> t decreasing).
   float t = 4.4721e-4f;  // acos(1 - 1e-7)
-  float ct = cosf(t);
-  float f = asinf(A * ct) + asinf(B * ct) + 2.f * t - CUDART_PI_F + G;
+  float ct = cos_(t);
+  float f = asin_(A * ct) + asin_(B * ct) + 2.f * t - CUDART_PI_F + G;
   if (f > 0.f) return 0.f;
   int it = 0;
+  #pragma unroll 1
   for (; it < 20 && fabsf(f) > 1e-6f; it++) {
-    const float st = sinf(t);
+    const float st = sin_(t);
     const float dg = 2.f - st * (A / fmaxf(1e-12f, sqrtf(1.f - ct * ct * A * A)) + B / fmaxf(1e-12f, sqrtf(1.f - ct * ct * B * B)));
     if (dg < 1e-12f) return 0.f;
     const float t1 = t - f / dg;
     if (t1 < t) return 0.f;
-    t = t1; ct = cosf(t);
-    f = asinf(A * ct) + asinf(B * ct) + 2.f * t - CUDART_PI_F + G;
+    t = t1; ct = cos_(t);
+    f = asin_(A * ct) + asin_(B * ct) + 2.f * t - CUDART_PI_F + G;
     if (f > 1e-5f) return 0.f;
   }
   if (it >= 20) return 0.f;
   float vx, vy, ang;
-  if (d[0] * d[3] - d[1] * d[2] > 0.f) { vx = d[0] / l0; vy = d[1] / l0; ang = 0.5f * CUDART_PI_F - t - asinf(A * ct); }
-  else { vx = d[2] / l1; vy = d[3] / l1; ang = 0.5f * CUDART_PI_F - t - asinf(B * ct); }
-  float sn, cs; sincosf(ang, &sn, &cs);
+  if (d[0] * d[3] - d[1] * d[2] > 0.f) { vx = d[0] / l0; vy = d[1] / l0; ang = 0.5f * CUDART_PI_F - t - asin_(A * ct); }
+  else { vx = d[2] / l1; vy = d[3] / l1; ang = 0.5f * CUDART_PI_F - t - asin_(B * ct); }
+  float sn, cs; sincos_(ang, &sn, &cs);
   pnt[0] = pnt[2] = rad * (cs * vx - sn * vy);
   pnt[1] = pnt[3] = rad * (sn * vx + cs * vy);
   return 0.f;
 }
 // returns wrap length or -1; w0/w1 = world tangent points
-__device__ float wrapGeom(f3 x0, f3 x1, f3 gpos, const float* gmat, float radius, int type, bool hasSide, f3 side, f3* w0, f3* w1) {
+__device__ __noinline__ float wrapGeom(f3 x0, f3 x1, f3 gpos, const float* gmat, float radius, int type, bool hasSide, f3 side, f3* w0, f3* w1) {
   if (radius < MINVAL) return -1.f;
   const f3 p0 = mulMT(gmat, x0 - gpos), p1 = mulMT(gmat, x1 - gpos);
   if (norm3(p0) < MINVAL || norm3(p1) < MINVAL) return -1.f;
@@ -443,7 +474,9 @@ __device__ float wrapGeom(f3 x0, f3 x1, f3 gpos, const float* gmat, float radius
 }
 
 // mj_tendon: path lengths + sparse moment arms
-__device__ void tendons(const DevModel& D, const SmemLayout& L, const FieldPtrs& F, float* sm, int lane, size_t w) {
+__device__ __noinline__ void tendons(int slot, int fslot, float* sm, int lane, size_t w) {
+  const DevModel& D = cP[slot].D; const SmemLayout& L = cP[slot].L; const FieldPtrs& F = cP[fslot].F;
+  #pragma unroll 1
   for (int u = lane; u < D.nunit; u += 32) {
     const int s0 = D.unit_s0[u], s1 = D.unit_s1[u], g = D.unit_geom[u];
     const int f0 = D.site_frame[s0], f1 = D.site_frame[s1];
@@ -474,8 +507,10 @@ __device__ void tendons(const DevModel& D, const SmemLayout& L, const FieldPtrs&
     sm[L.uwrap + u] = wlen < 0.f ? 0.f : 1.f;
   }
   __syncwarp();
+  #pragma unroll 1
   for (int n = lane; n < D.nnz; n += 32) {
     float acc = 0.f;
+    #pragma unroll 1
     for (int e = D.nz_estart[n]; e < D.nz_estart[n + 1]; e++) {
       const int kind = D.ent_kind[e];
       if (kind != ENT_ALWAYS) {
@@ -490,8 +525,10 @@ __device__ void tendons(const DevModel& D, const SmemLayout& L, const FieldPtrs&
     }
     sm[L.tenJ + n] = acc;
   }
+  #pragma unroll 1
   for (int t = lane; t < D.nten; t += 32) {
     float acc = 0.f;
+    #pragma unroll 1
     for (int u = D.ten_ustart[t]; u < D.ten_ustart[t + 1]; u++) acc += sm[L.ulen + u];
     sm[L.tenlen + t] = acc;
   }
@@ -500,53 +537,69 @@ __device__ void tendons(const DevModel& D, const SmemLayout& L, const FieldPtrs&
   if (tl) for (int t = lane; t < D.nten; t += 32) tl[w * D.nten + t] = sm[L.tenlen + t];
   if (tj) {
     const size_t n = (size_t)D.nten * D.nv;
+    #pragma unroll 1
     for (int i = lane; i < (int)n; i += 32) tj[w * n + i] = 0.f;
     __syncwarp();
+    #pragma unroll 1
     for (int k = lane; k < D.nnz; k += 32) tj[w * n + (size_t)D.nz_tendon[k] * D.nv + D.nz_dof[k]] = sm[L.tenJ + k];
   }
 }
 
 // ------------------------------------------------------------------------------------------ inertia: mj_crb, mj_factorM, mj_solveM
 // sparse L^T D L in place over the dof-tree pattern; one precomputed multiply-subtract list per column
-__device__ void factorLDL(const DevModel& D, float* LD, float* dinv, int lane) {
+__device__ __noinline__ void factorLDL(int slot, float* LD, float* dinv, int lane) {
+  const DevModel& D = cP[slot].D;
   const int nv = D.nv;
+  #pragma unroll 1
   for (int pos = 0; pos < nv; pos++) {
     const int k = nv - 1 - pos, akk = D.dof_Madr[k];
     const float inv = 1.f / LD[akk];
+    #pragma unroll 1
     for (int o = D.ldl_start[pos] + lane; o < D.ldl_start[pos + 1]; o += 32) LD[D.ldl_dst[o]] -= LD[D.ldl_a[o]] * LD[D.ldl_b[o]] * inv;
     __syncwarp();
     const int d = D.dof_rowlen[k];
+    #pragma unroll 1
     for (int s = 1 + lane; s < d; s += 32) LD[akk + s] *= inv;
     if (lane == 0) dinv[k] = inv;
     __syncwarp();
   }
 }
 // x <- (L^T D L)^-1 x, by dof-tree levels
-__device__ void solveLDL(const DevModel& D, const float* LD, const float* dinv, float* x, int lane) {
+__device__ __noinline__ void solveLDL(int slot, const float* LD, const float* dinv, float* x, int lane) {
+  const DevModel& D = cP[slot].D;
+  #pragma unroll 1
   for (int l = D.ndlevel - 1; l >= 0; l--) {
+    #pragma unroll 1
     for (int idx = D.dlvl_start[l] + lane; idx < D.dlvl_start[l + 1]; idx += 32) {
       const int j = D.dlvl_dofs[idx];
       float acc = x[j];
+      #pragma unroll 1
       for (int e = D.desc_start[j]; e < D.desc_start[j + 1]; e++) acc -= LD[D.desc_idx[e]] * x[D.desc_dof[e]];
       x[j] = acc;
     }
     __syncwarp();
   }
+  #pragma unroll 1
   for (int i = lane; i < D.nv; i += 32) x[i] *= dinv[i];
   __syncwarp();
+  #pragma unroll 1
   for (int l = 1; l < D.ndlevel; l++) {
+    #pragma unroll 1
     for (int idx = D.dlvl_start[l] + lane; idx < D.dlvl_start[l + 1]; idx += 32) {
       const int i = D.dlvl_dofs[idx], a = D.dof_Madr[i], d = D.dof_rowlen[i];
       float acc = x[i];
+      #pragma unroll 1
       for (int s = 1; s < d; s++) acc -= LD[a + s] * x[D.M_col[a + s]];
       x[i] = acc;
     }
     __syncwarp();
   }
 }
-__device__ void inertia(const DevModel& D, const SmemLayout& L, const FieldPtrs& F, float* sm, int lane, size_t w) {
+__device__ __noinline__ void inertia(int slot, int fslot, float* sm, int lane, size_t w) {
+  const DevModel& D = cP[slot].D; const SmemLayout& L = cP[slot].L; const FieldPtrs& F = cP[fslot].F;
   const int nv = D.nv;
   // composite inertia of each frame's subtree (frames are in DFS order: subtree = contiguous range)
+  #pragma unroll 1
   for (int i = lane; i < 10 * D.nframe; i += 32) {
     const int f = i / 10, k = i - 10 * f;
     float acc = 0.f;
@@ -555,8 +608,10 @@ __device__ void inertia(const DevModel& D, const SmemLayout& L, const FieldPtrs&
   }
   __syncwarp();
   float* f6 = sm + L.cdof_dot;  // scratch until the velocity stage
+  #pragma unroll 1
   for (int i = lane; i < nv; i += 32) inertMulVec(f6 + 6 * i, sm + L.crb + 10 * D.dof_frame[i], sm + L.cdof + 6 * i);
   __syncwarp();
+  #pragma unroll 1
   for (int e = lane; e < D.nM; e += 32) {
     const int r = D.M_row[e], c = D.M_col[e];
     const float* a = sm + L.cdof + 6 * c; const float* b = f6 + 6 * r;
@@ -565,12 +620,14 @@ __device__ void inertia(const DevModel& D, const SmemLayout& L, const FieldPtrs&
     sm[L.qM + e] = s; sm[L.qLD + e] = s;
   }
   __syncwarp();
-  factorLDL(D, sm + L.qLD, sm + L.qLDinv, lane);
+  factorLDL(slot, sm + L.qLD, sm + L.qLDinv, lane);
   float* qMo = (float*)F.p[MYO_F_QM]; float* qLDo = (float*)F.p[MYO_F_QLD]; float* qdi = (float*)F.p[MYO_F_QLDIAGINV];
   if (qMo || qLDo) {
     const size_t n = (size_t)nv * nv;
+    #pragma unroll 1
     for (int i = lane; i < (int)n; i += 32) { if (qMo) qMo[w * n + i] = 0.f; if (qLDo) qLDo[w * n + i] = 0.f; }
     __syncwarp();
+    #pragma unroll 1
     for (int e = lane; e < D.nM; e += 32) {
       const int r = D.M_row[e], c = D.M_col[e];
       if (qMo) { qMo[w * n + r * nv + c] = sm[L.qM + e]; qMo[w * n + c * nv + r] = sm[L.qM + e]; }
@@ -581,19 +638,24 @@ __device__ void inertia(const DevModel& D, const SmemLayout& L, const FieldPtrs&
 }
 
 // ------------------------------------------------------------------------------------------ mj_fwdVelocity
-__device__ void velocity(const DevModel& D, const SmemLayout& L, const FieldPtrs& F, float* sm, int lane, size_t w) {
+__device__ __noinline__ void velocity(int slot, int fslot, float* sm, int lane, size_t w) {
+  const DevModel& D = cP[slot].D; const SmemLayout& L = cP[slot].L; const FieldPtrs& F = cP[fslot].F;
   const int nv = D.nv;
   const float* qvel = sm + L.qvel;
+  #pragma unroll 1
   for (int t = lane; t < D.nten; t += 32) {
     float acc = 0.f;
+    #pragma unroll 1
     for (int n = D.ten_nzstart[t]; n < D.ten_nzstart[t + 1]; n++) acc += sm[L.tenJ + n] * qvel[D.nz_dof[n]];
     sm[L.tenvel + t] = acc;
   }
   // body velocities: sum of the ancestor dof motions (all expressed about the tree's centre of mass)
+  #pragma unroll 1
   for (int f = lane; f < D.nframe; f += 32) {
     float v[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     if (f > 0) {
       const int last = D.fr_dofadr[f] + D.fr_dofnum[f] - 1, a = D.dof_Madr[last], d = D.dof_rowlen[last];
+      #pragma unroll 1
       for (int s = d - 1; s >= 0; s--) {
         const int j = D.M_col[a + s]; const float qv = qvel[j]; const float* cd = sm + L.cdof + 6 * j;
 #pragma unroll
@@ -603,11 +665,13 @@ __device__ void velocity(const DevModel& D, const SmemLayout& L, const FieldPtrs
 #pragma unroll
     for (int k = 0; k < 6; k++) sm[L.cvel + 6 * f + k] = v[k];
   }
+  #pragma unroll 1
   for (int i = lane; i < nv; i += 32) {
     const int pc = D.dof_prevcount[i], a = D.dof_Madr[i], d = D.dof_rowlen[i];
     float* out = sm + L.cdof_dot + 6 * i;
     if (pc < 0) { for (int k = 0; k < 6; k++) out[k] = 0.f; continue; }
     float v[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    #pragma unroll 1
     for (int s = d - 1; s >= pc; s--) {
       const int j = D.M_col[a + s]; const float qv = qvel[j]; const float* cd = sm + L.cdof + 6 * j;
 #pragma unroll
@@ -617,10 +681,12 @@ __device__ void velocity(const DevModel& D, const SmemLayout& L, const FieldPtrs
   }
   __syncwarp();
   const bool grav = !(D.disableflags & DSBL_GRAVITY);
+  #pragma unroll 1
   for (int f = lane; f < D.nframe; f += 32) {
     if (f == 0) { for (int k = 0; k < 6; k++) sm[L.cacc + k] = 0.f; continue; }
     float a6[6] = {0.f, 0.f, 0.f, grav ? -D.gravity[0] : 0.f, grav ? -D.gravity[1] : 0.f, grav ? -D.gravity[2] : 0.f};
     const int last = D.fr_dofadr[f] + D.fr_dofnum[f] - 1, a = D.dof_Madr[last], d = D.dof_rowlen[last];
+    #pragma unroll 1
     for (int s = d - 1; s >= 0; s--) {
       const int j = D.M_col[a + s]; const float qv = qvel[j]; const float* cd = sm + L.cdof_dot + 6 * j;
 #pragma unroll
@@ -635,9 +701,11 @@ __device__ void velocity(const DevModel& D, const SmemLayout& L, const FieldPtrs
   }
   __syncwarp();
   const bool passive_on = !(D.disableflags & DSBL_PASSIVE);
+  #pragma unroll 1
   for (int i = lane; i < nv; i += 32) {
     const int f = D.dof_frame[i];
     float acc[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    #pragma unroll 1
     for (int g = f; g < D.fr_subend[f]; g++)
 #pragma unroll
       for (int k = 0; k < 6; k++) acc[k] += sm[L.cacc + 6 * g + k];
@@ -650,6 +718,7 @@ __device__ void velocity(const DevModel& D, const SmemLayout& L, const FieldPtrs
       if (k != 0.f && D.jnt_type[j] >= JNT_SLIDE) spring = -k * (sm[L.qpos + D.jnt_qposadr[j]] - D.qpos_spring[D.jnt_qposadr[j]]);
       damper = -D.dof_damping[i] * qvel[i];
       if (D.any_tendon_passive)
+        #pragma unroll 1
         for (int c = D.col_start[i]; c < D.col_start[i + 1]; c++) {
           const int n = D.col_nz[c], t = D.nz_tendon[n];
           const float ks = D.ten_stiffness[t], kd = D.ten_damping[t], len = sm[L.tenlen + t];
@@ -686,7 +755,7 @@ __device__ __forceinline__ float muscleFL(float Ln, float lmin, float lmax) {
   x = (lmax - Ln) / fmaxf(MINVAL, lmax - b);
   return 0.5f * x * x;
 }
-__device__ void muscleGainBias(float len, float vel, const float* lr, float acc0, const float* prm, float* gain, float* bias) {
+__device__ __noinline__ void muscleGainBias(float len, float vel, const float* lr, float acc0, const float* prm, float* gain, float* bias) {
   const float r0 = prm[0], r1 = prm[1], scale = prm[3], lmin = prm[4], lmax = prm[5], vmax = prm[6], fpmax = prm[7], fvmax = prm[8];
   float force = prm[2];
   if (force < 0.f) force = scale / fmaxf(MINVAL, acc0);
@@ -706,9 +775,11 @@ __device__ void muscleGainBias(float len, float vel, const float* lr, float acc0
   else if (Ln <= b) { const float x = (Ln - 1.f) / fmaxf(MINVAL, b - 1.f); *bias = -force * fpmax * 0.5f * x * x; }
   else { const float x = (Ln - b) / fmaxf(MINVAL, b - 1.f); *bias = -force * fpmax * (0.5f + x); }
 }
-__device__ void actuation(const DevModel& D, const SmemLayout& L, const FieldPtrs& F, float* sm, int lane, size_t w) {
+__device__ __noinline__ void actuation(int slot, int fslot, float* sm, int lane, size_t w) {
+  const DevModel& D = cP[slot].D; const SmemLayout& L = cP[slot].L; const FieldPtrs& F = cP[fslot].F;
   const int nu = D.nu, nv = D.nv;
   const bool on = !(D.disableflags & DSBL_ACTUATION);
+  #pragma unroll 1
   for (int i = lane; i < nu; i += 32) {
     const int id = D.act_trnid[i];
     const float gear = D.act_gear[i];
@@ -753,22 +824,27 @@ __device__ void actuation(const DevModel& D, const SmemLayout& L, const FieldPtr
     if (aa >= 0) sm[L.actdot + aa] = adot;
   }
   __syncwarp();
+  #pragma unroll 1
   for (int t = lane; t < D.nten; t += 32) {
     float acc = 0.f;
+    #pragma unroll 1
     for (int k = D.tact_start[t]; k < D.tact_start[t + 1]; k++) { const int a = D.tact_list[k]; acc += D.act_gear[a] * sm[L.actforce + a]; }
     sm[L.tforce + t] = acc;
   }
   __syncwarp();
+  #pragma unroll 1
   for (int i = lane; i < nv; i += 32) {
     float acc = 0.f;
+    #pragma unroll 1
     for (int c = D.col_start[i]; c < D.col_start[i + 1]; c++) { const int n = D.col_nz[c]; acc += sm[L.tenJ + n] * sm[L.tforce + D.nz_tendon[n]]; }
+    #pragma unroll 1
     for (int k = D.dact_start[i]; k < D.dact_start[i + 1]; k++) { const int a = D.dact_list[k]; acc += D.act_gear[a] * sm[L.actforce + a]; }
     sm[L.qfrc_act + i] = acc;
     sm[L.smooth + i] = sm[L.passive + i] - sm[L.bias + i] + acc;
     sm[L.qacc_smooth + i] = sm[L.smooth + i];
   }
   __syncwarp();
-  solveLDL(D, sm + L.qLD, sm + L.qLDinv, sm + L.qacc_smooth, lane);
+  solveLDL(slot, sm + L.qLD, sm + L.qLDinv, sm + L.qacc_smooth, lane);
   float* o;
   if ((o = (float*)F.p[MYO_F_ACTUATOR_LENGTH])) for (int i = lane; i < nu; i += 32) o[w * nu + i] = sm[L.actlen + i];
   if ((o = (float*)F.p[MYO_F_ACTUATOR_VELOCITY])) for (int i = lane; i < nu; i += 32) o[w * nu + i] = sm[L.actvel + i];
@@ -779,8 +855,10 @@ __device__ void actuation(const DevModel& D, const SmemLayout& L, const FieldPtr
   if ((o = (float*)F.p[MYO_F_QACC_SMOOTH])) for (int i = lane; i < nv; i += 32) o[w * nv + i] = sm[L.qacc_smooth + i];
   if ((o = (float*)F.p[MYO_F_ACTUATOR_MOMENT])) {
     const size_t n = (size_t)nu * nv;
+    #pragma unroll 1
     for (int i = lane; i < (int)n; i += 32) o[w * n + i] = 0.f;
     __syncwarp();
+    #pragma unroll 1
     for (int a = 0; a < nu; a++) {   // rows are sparse copies of the tendon rows
       const int id = D.act_trnid[a];
       if (D.act_trntype[a] == 3) { for (int k = D.ten_nzstart[id] + lane; k < D.ten_nzstart[id + 1]; k += 32) o[w * n + (size_t)a * nv + D.nz_dof[k]] = D.act_gear[a] * sm[L.tenJ + k]; }
@@ -791,7 +869,7 @@ __device__ void actuation(const DevModel& D, const SmemLayout& L, const FieldPtr
 
 // ------------------------------------------------------------------------------------------ collision
 struct Shape { int type; f3 pos; const float* mat; f3 size; float margin; };
-__device__ f3 supportPt(const Shape& s, f3 dir) {
+__device__ __noinline__ f3 supportPt(const Shape& s, f3 dir) {
   const f3 d = mulMT(s.mat, dir);
   f3 r = mk3(0.f, 0.f, 0.f);
   switch (s.type) {
@@ -812,11 +890,11 @@ __device__ f3 supportPt(const Shape& s, f3 dir) {
   return mulM(s.mat, r) + s.pos + dir * s.margin;
 }
 struct Sup { f3 v, a, b; };
-__device__ __forceinline__ Sup mprSup(const Shape& A, const Shape& B, f3 d) {
+__device__ __noinline__ Sup mprSup(const Shape& A, const Shape& B, f3 d) {
   Sup s; s.a = supportPt(A, d * -1.f); s.b = supportPt(B, d); s.v = s.b - s.a; return s;
 }
 // Minkowski portal refinement on B - A (same statement as oracle/mjstep_oracle.cpp, float32)
-__device__ bool mprPenetration(const Shape& A, const Shape& B, float tol, int maxit, float* depth, f3* nrm, f3* pos) {
+__device__ __noinline__ bool mprPenetration(const Shape& A, const Shape& B, float tol, int maxit, float* depth, f3* nrm, f3* pos) {
   f3 v0 = B.pos - A.pos;
   if (norm3(v0) < 1e-12f) v0 = mk3(1e-5f, 0.f, 0.f);
   f3 dir = unit3(v0 * -1.f);
@@ -834,6 +912,7 @@ __device__ bool mprPenetration(const Shape& A, const Shape& B, float tol, int ma
   dir = unit3(cross(s1.v - v0, s2.v - v0));
   if (dot(dir, v0) > 0.f) { Sup t = s1; s1 = s2; s2 = t; dir = dir * -1.f; }
   Sup s3;
+  #pragma unroll 1
   for (int it = 0;; it++) {
     if (it > maxit) return false;
     s3 = mprSup(A, B, dir);
@@ -843,6 +922,7 @@ __device__ bool mprPenetration(const Shape& A, const Shape& B, float tol, int ma
     break;
   }
   bool hit = false;
+  #pragma unroll 1
   for (int it = 0;; it++) {
     dir = unit3(cross(s2.v - s1.v, s3.v - s1.v));
     if (dot(dir, s1.v) >= 0.f) hit = true;
@@ -876,7 +956,8 @@ __device__ __forceinline__ Hit sphereSphere(f3 c1, float r1, f3 c2, float r2) {
   return h;
 }
 // narrow phase for one candidate pair; returns the number of contacts (0..2) with dist < margin
-__device__ int collidePair(const DevModel& D, const SmemLayout& L, const float* sm, int pr, Hit* h) {
+__device__ __noinline__ int collidePair(int slot, const float* sm, int pr, Hit* h) {
+  const DevModel& D = cP[slot].D; const SmemLayout& L = cP[slot].L;
   const int c1 = D.pair_cg1[pr], c2 = D.pair_cg2[pr];
   const int t1 = D.cg_type[c1], t2 = D.cg_type[c2];
   const float margin = D.pair_prm[16 * pr];
@@ -890,6 +971,7 @@ __device__ int collidePair(const DevModel& D, const SmemLayout& L, const float* 
     if (dot(p2 - p1, ax1) > D.cg_rbound[c2] + margin) return 0;
     if (t2 == G_SPHERE || t2 == G_CAPSULE) {
       const int cnt = t2 == G_SPHERE ? 1 : 2;
+      #pragma unroll 1
       for (int k = 0; k < cnt; k++) {
         const f3 c = t2 == G_SPHERE ? p2 : (k == 0 ? p2 + ax2 * sz2.y : p2 - ax2 * sz2.y);
         const float dist = dot(c - p1, ax1) - sz2.x;
@@ -937,8 +1019,10 @@ __device__ __forceinline__ void makeFrame(f3 n, f3* y, f3* z) {
   *y = t; *z = cross(n, t);
 }
 // returns the number of contacts; contact record: dist, pos[3], normal[3], pair, efc_address, dim, spare[2]
-__device__ int collision(const DevModel& D, const SmemLayout& L, float* sm, int lane, int* status) {
+__device__ __noinline__ int collision(int slot, float* sm, int lane, int* status) {
+  const DevModel& D = cP[slot].D; const SmemLayout& L = cP[slot].L;
   if (D.npair == 0) return 0;
+  #pragma unroll 1
   for (int c = lane; c < D.ncg; c += 32) {
     const int f = D.cg_frame[c];
     const float* R = FR_MAT(sm, L, f); const float* lm = D.cg_lmat + 9 * c;
@@ -951,16 +1035,18 @@ __device__ int collision(const DevModel& D, const SmemLayout& L, float* sm, int 
   }
   __syncwarp();
   int ncon = 0;
+  #pragma unroll 1
   for (int base = 0; base < D.npair; base += 32) {
     const int pr = base + lane;
     Hit h[2]; int n = 0;
-    if (pr < D.npair) n = collidePair(D, L, sm, pr, h);
+    if (pr < D.npair) n = collidePair(slot, sm, pr, h);
     // exclusive scan of the per-lane contact counts keeps the pair order
     int incl = n;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(FULLMASK, incl, o); if (lane >= o) incl += t; }
     const int total = __shfl_sync(FULLMASK, incl, 31);
     int at = ncon + incl - n;
+    #pragma unroll 1
     for (int k = 0; k < n; k++, at++) {
       if (at >= D.nconmax) continue;
       float* c = sm + L.con + 12 * at;
@@ -979,7 +1065,7 @@ enum { E_D = 0, E_AREF, E_JAR, E_JV, E_FORCE, E_DESC0, E_COEF, E_DESC1, E_POS, E
 #define EFC(k, r) sm[L.efc + (k) * D.njmax + (r)]
 #define EFCI(k, r) __float_as_int(sm[L.efc + (k) * D.njmax + (r)])
 
-__device__ __forceinline__ float impedance(const float* si, float x) {  // si = sanitised solimp, x = |pos - margin|
+__device__ __noinline__ float impedance(const float* si, float x) {  // si = sanitised solimp, x = |pos - margin|
   const float dmin = si[0], dmax = si[1], width = si[2], mid = si[3], power = si[4];
   if (dmin == dmax || width <= MINVAL) return 0.5f * (dmin + dmax);
   x = x / width;
@@ -987,12 +1073,13 @@ __device__ __forceinline__ float impedance(const float* si, float x) {  // si = 
   if (x <= 0.f) return dmin;
   float y;
   if (power == 1.f) y = x;
-  else if (x <= mid) y = powf(x, power) / powf(mid, power - 1.f);
-  else y = 1.f - powf(1.f - x, power) / powf(1.f - mid, power - 1.f);
+  else if (x <= mid) y = pow_(x, power) / pow_(mid, power - 1.f);
+  else y = 1.f - pow_(1.f - x, power) / pow_(1.f - mid, power - 1.f);
   return dmin + y * (dmax - dmin);
 }
-__device__ __forceinline__ void setRow(const DevModel& D, const SmemLayout& L, float* sm, int r, int type, int id, float coef, int desc1,
+__device__ __noinline__ void setRow(int slot, float* sm, int r, int type, int id, float coef, int desc1,
                                        float pos, float margin, float dA, const float* kb, float vel, float Rscale) {
+  const DevModel& D = cP[slot].D; const SmemLayout& L = cP[slot].L;
   // kb: K, B, solimp[5]
   const float imp = impedance(kb + 2, fabsf(pos - margin));
   float R = fmaxf(MINVAL, (1.f - imp) * dA / imp);
@@ -1010,17 +1097,21 @@ __device__ __forceinline__ int warpExclScan(int v, int lane, int* total) {
   return incl - v;
 }
 // base-row products  out[b] = conJ[b] . x   for the nb*ncon contact base rows
-__device__ __forceinline__ void baseMul(const DevModel& D, const SmemLayout& L, float* sm, int lane, int ncon, const float* x, float* out) {
+__device__ __noinline__ void baseMul(int slot, float* sm, int lane, int ncon, const float* x, float* out) {
+  const DevModel& D = cP[slot].D; const SmemLayout& L = cP[slot].L;
   const int nbr = D.maxbase * ncon, nv = D.nv;
+  #pragma unroll 1
   for (int b = lane; b < nbr; b += 32) {
     const float* J = sm + L.conJ + b * nv;
     float acc = 0.f;
+    #pragma unroll 1
     for (int k = 0; k < nv; k++) acc = fmaf(J[k], x[k], acc);
     out[b] = acc;
   }
 }
 // out[r] = J_r . x for every efc row (bx = base products of x)
-__device__ __forceinline__ float rowMul(const DevModel& D, const SmemLayout& L, const float* sm, int r, const float* x, const float* bx) {
+__device__ __noinline__ float rowMul(int slot, const float* sm, int r, const float* x, const float* bx) {
+  const DevModel& D = cP[slot].D; const SmemLayout& L = cP[slot].L;
   const int d0 = EFCI(E_DESC0, r), type = d0 & 3, id = d0 >> 2;
   const float coef = EFC(E_COEF, r);
   if (type == ROW_LIMJ) return coef * x[D.limj_dof[id]];
@@ -1028,16 +1119,19 @@ __device__ __forceinline__ float rowMul(const DevModel& D, const SmemLayout& L, 
   if (type == ROW_EQ) { const int d2 = D.eq_dof2[id]; return x[D.eq_dof1[id]] + (d2 >= 0 ? coef * x[d2] : 0.f); }
   const int t = D.limt_ten[id];
   float acc = 0.f;
+  #pragma unroll 1
   for (int n = D.ten_nzstart[t]; n < D.ten_nzstart[t + 1]; n++) acc += sm[L.tenJ + n] * x[D.nz_dof[n]];
   return coef * acc;
 }
 
-__device__ int makeConstraint(const DevModel& D, const SmemLayout& L, float* sm, int lane, int ncon, int* status) {
+__device__ __noinline__ int makeConstraint(int slot, float* sm, int lane, int ncon, int* status) {
+  const DevModel& D = cP[slot].D; const SmemLayout& L = cP[slot].L;
   const int nv = D.nv, njmax = D.njmax;
   const float* qpos = sm + L.qpos; const float* qvel = sm + L.qvel;
   int nefc = 0;
   if (D.disableflags & DSBL_CONSTRAINT) return 0;
   // ---- equality rows (always active)
+  #pragma unroll 1
   for (int e = lane; e < D.neq; e += 32) {
     const int d1 = D.eq_dof1[e], d2 = D.eq_dof2[e], q1 = D.eq_q1[e], q2 = D.eq_q2[e];
     const float* dt = D.eq_data + 5 * e;
@@ -1048,11 +1142,12 @@ __device__ int makeConstraint(const DevModel& D, const SmemLayout& L, float* sm,
       dpoly = dt[1] + x * (2.f * dt[2] + x * (3.f * dt[3] + x * 4.f * dt[4]));
       vel -= dpoly * qvel[d2];
     } else pos = qpos[q1] - D.qpos0[q1] - dt[0];
-    setRow(D, L, sm, e, ROW_EQ, e, -dpoly, 0, pos, 0.f, D.eq_prm[8 * e + 7], D.eq_prm + 8 * e, vel, 0.f);
+    setRow(slot, sm, e, ROW_EQ, e, -dpoly, 0, pos, 0.f, D.eq_prm[8 * e + 7], D.eq_prm + 8 * e, vel, 0.f);
   }
   nefc = D.neq;
   // ---- joint limits, then tendon limits
   const int nlim = D.nlimj + D.nlimt;
+  #pragma unroll 1
   for (int base = 0; base < nlim; base += 32) {
     const int li = base + lane;
     float dlo = 1.f, dhi = 1.f, margin = 0.f; int cnt = 0;
@@ -1069,8 +1164,8 @@ __device__ int makeConstraint(const DevModel& D, const SmemLayout& L, float* sm,
       int r0 = -1, r1 = -1;
       const float v = isj ? qvel[D.limj_dof[li]] : sm[L.tenvel + D.limt_ten[li - D.nlimj]];
       const int id = isj ? li : li - D.nlimj, type = isj ? ROW_LIMJ : ROW_LIMT;
-      if (dlo < margin) { if (at < njmax) { r0 = at; setRow(D, L, sm, at, type, id, 1.f, 0, dlo, margin, prm[10], prm + 3, v, 0.f); } at++; }
-      if (dhi < margin) { if (at < njmax) { r1 = at; setRow(D, L, sm, at, type, id, -1.f, 0, dhi, margin, prm[10], prm + 3, -v, 0.f); } at++; }
+      if (dlo < margin) { if (at < njmax) { r0 = at; setRow(slot, sm, at, type, id, 1.f, 0, dlo, margin, prm[10], prm + 3, v, 0.f); } at++; }
+      if (dhi < margin) { if (at < njmax) { r1 = at; setRow(slot, sm, at, type, id, -1.f, 0, dhi, margin, prm[10], prm + 3, -v, 0.f); } at++; }
       sm[L.limrow + 2 * li] = __int_as_float(r0); sm[L.limrow + 2 * li + 1] = __int_as_float(r1);
     }
     nefc += total;
@@ -1079,6 +1174,7 @@ __device__ int makeConstraint(const DevModel& D, const SmemLayout& L, float* sm,
   if (ncon > 0) {
     const int nb = D.maxbase;
     int adr_of_lane = -1;
+    #pragma unroll 1
     for (int base = 0; base < ncon; base += 32) {   // nconmax may exceed 32
       const int c = base + lane;
       int rows = 0;
@@ -1094,12 +1190,14 @@ __device__ int makeConstraint(const DevModel& D, const SmemLayout& L, float* sm,
     }
     __syncwarp();
     // base Jacobian rows, one contact at a time, lanes over dofs
+    #pragma unroll 1
     for (int c = 0; c < ncon; c++) {
       const float* cr = sm + L.con + 12 * c;
       const int pr = __float_as_int(cr[7]);
       const int f1 = D.cg_frame[D.pair_cg1[pr]], f2 = D.cg_frame[D.pair_cg2[pr]];
       const f3 pos = ld3(cr + 1), n = ld3(cr + 4);
       f3 y, z; makeFrame(n, &y, &z);
+      #pragma unroll 1
       for (int k = lane; k < nv; k += 32) {
         const int in1 = (D.fr_mask[2 * f1 + (k >> 5)] >> (k & 31)) & 1, in2 = (D.fr_mask[2 * f2 + (k >> 5)] >> (k & 31)) & 1;
         const float s = (float)(in2 - in1);
@@ -1117,8 +1215,9 @@ __device__ int makeConstraint(const DevModel& D, const SmemLayout& L, float* sm,
     }
     __syncwarp();
     float* bx = sm + L.basev;
-    baseMul(D, L, sm, lane, ncon, qvel, bx);
+    baseMul(slot, sm, lane, ncon, qvel, bx);
     __syncwarp();
+    #pragma unroll 1
     for (int c = lane; c < ncon; c += 32) {
       const float* cr = sm + L.con + 12 * c;
       const int adr = __float_as_int(cr[8]);
@@ -1130,15 +1229,16 @@ __device__ int makeConstraint(const DevModel& D, const SmemLayout& L, float* sm,
       const float tran = D.cg_invweight[2 * c1] + D.cg_invweight[2 * c2];
       float kb[7] = {pp[14], pp[15], pp[9], pp[10], pp[11], pp[12], pp[13]};
       const int bn = c * nb;
-      if (dim == 1) setRow(D, L, sm, adr, ROW_CON, bn, 0.f, -1, dist, margin, tran, kb, bx[bn], 0.f);
+      if (dim == 1) setRow(slot, sm, adr, ROW_CON, bn, 0.f, -1, dist, margin, tran, kb, bx[bn], 0.f);
       else {
         const float mu0 = pp[2] * rsqrtf(D.impratio);
         const float dA0 = tran + pp[2] * pp[2] * tran;   // first pyramid row sets the shared regulariser
+        #pragma unroll 1
         for (int k = 1; k < dim; k++) {
           const float mu = pp[1 + k];
           const int bt = bn + k;
-          setRow(D, L, sm, adr + 2 * (k - 1), ROW_CON, bn, mu, bt, dist, margin, dA0, kb, bx[bn] + mu * bx[bt], 2.f * mu0 * mu0);
-          setRow(D, L, sm, adr + 2 * (k - 1) + 1, ROW_CON, bn, -mu, bt, dist, margin, dA0, kb, bx[bn] - mu * bx[bt], 2.f * mu0 * mu0);
+          setRow(slot, sm, adr + 2 * (k - 1), ROW_CON, bn, mu, bt, dist, margin, dA0, kb, bx[bn] + mu * bx[bt], 2.f * mu0 * mu0);
+          setRow(slot, sm, adr + 2 * (k - 1) + 1, ROW_CON, bn, -mu, bt, dist, margin, dA0, kb, bx[bn] - mu * bx[bt], 2.f * mu0 * mu0);
         }
       }
     }
@@ -1149,23 +1249,29 @@ __device__ int makeConstraint(const DevModel& D, const SmemLayout& L, float* sm,
 }
 
 // ------------------------------------------------------------------------------------------ Newton solver (mj_fwdConstraint)
-__device__ __forceinline__ void mulMsparse(const DevModel& D, const float* qM, const float* x, float* out, int lane) {
+__device__ __noinline__ void mulMsparse(int slot, const float* qM, const float* x, float* out, int lane) {
+  const DevModel& D = cP[slot].D;
+  #pragma unroll 1
   for (int i = lane; i < D.nv; i += 32) {
     const int a = D.dof_Madr[i], d = D.dof_rowlen[i];
     float acc = 0.f;
+    #pragma unroll 1
     for (int s = 0; s < d; s++) acc = fmaf(qM[a + s], x[D.M_col[a + s]], acc);
+    #pragma unroll 1
     for (int e = D.desc_start[i]; e < D.desc_start[i + 1]; e++) acc = fmaf(qM[D.desc_idx[e]], x[D.desc_dof[e]], acc);
     out[i] = acc;
   }
 }
 // jar = J x - aref for all rows, returns (uniform) constraint cost; force/active are implied by jar
-__device__ float residualCost(const DevModel& D, const SmemLayout& L, float* sm, int lane, int ncon, int nefc, const float* x) {
+__device__ __noinline__ float residualCost(int slot, float* sm, int lane, int ncon, int nefc, const float* x) {
+  const DevModel& D = cP[slot].D; const SmemLayout& L = cP[slot].L;
   float* bx = sm + L.basev;
-  baseMul(D, L, sm, lane, ncon, x, bx);
+  baseMul(slot, sm, lane, ncon, x, bx);
   __syncwarp();
   float cost = 0.f;
+  #pragma unroll 1
   for (int r = lane; r < nefc; r += 32) {
-    const float jar = rowMul(D, L, sm, r, x, bx) - EFC(E_AREF, r);
+    const float jar = rowMul(slot, sm, r, x, bx) - EFC(E_AREF, r);
     EFC(E_JAR, r) = jar;
     const bool on = ((EFCI(E_DESC0, r) & 3) == ROW_EQ) || jar < 0.f;
     if (on) cost += 0.5f * EFC(E_D, r) * jar * jar;
@@ -1173,15 +1279,19 @@ __device__ float residualCost(const DevModel& D, const SmemLayout& L, float* sm,
   __syncwarp();
   return warpSum(cost);
 }
-__device__ __forceinline__ bool rowActive(const DevModel& D, const SmemLayout& L, const float* sm, int r) {
+__device__ __forceinline__ bool rowActive(int slot, const float* sm, int r) {
+  const DevModel& D = cP[slot].D; const SmemLayout& L = cP[slot].L;
   return ((EFCI(E_DESC0, r) & 3) == ROW_EQ) || EFC(E_JAR, r) < 0.f;
 }
 // forces from jar, then out = J^T f  (deterministic gathers, no atomics)
-__device__ void constraintForce(const DevModel& D, const SmemLayout& L, float* sm, int lane, int ncon, int nefc, float* out) {
+__device__ __noinline__ void constraintForce(int slot, float* sm, int lane, int ncon, int nefc, float* out) {
+  const DevModel& D = cP[slot].D; const SmemLayout& L = cP[slot].L;
   const int nv = D.nv, nb = D.maxbase;
-  for (int r = lane; r < nefc; r += 32) EFC(E_FORCE, r) = rowActive(D, L, sm, r) ? -EFC(E_D, r) * EFC(E_JAR, r) : 0.f;
+  #pragma unroll 1
+  for (int r = lane; r < nefc; r += 32) EFC(E_FORCE, r) = rowActive(slot, sm, r) ? -EFC(E_D, r) * EFC(E_JAR, r) : 0.f;
   __syncwarp();
   float* bf = sm + L.basev + nb * D.nconmax;
+  #pragma unroll 1
   for (int b = lane; b < nb * ncon; b += 32) {
     const int c = b / nb, k = b - c * nb;
     const float* cr = sm + L.con + 12 * c;
@@ -1195,8 +1305,10 @@ __device__ void constraintForce(const DevModel& D, const SmemLayout& L, float* s
     bf[b] = f;
   }
   __syncwarp();
+  #pragma unroll 1
   for (int k = lane; k < nv; k += 32) {
     float acc = 0.f;
+    #pragma unroll 1
     for (int e = D.dofeq_start[k]; e < D.dofeq_start[k + 1]; e++) {
       const int v = D.dofeq_list[e], r = v >> 1;
       acc += (v & 1) ? EFC(E_COEF, r) * EFC(E_FORCE, r) : EFC(E_FORCE, r);
@@ -1205,6 +1317,7 @@ __device__ void constraintForce(const DevModel& D, const SmemLayout& L, float* s
     if (li >= 0)
       for (int s = 0; s < 2; s++) { const int r = __float_as_int(sm[L.limrow + 2 * li + s]); if (r >= 0) acc += EFC(E_COEF, r) * EFC(E_FORCE, r); }
     if (D.nlimt > 0)
+      #pragma unroll 1
       for (int c = D.col_start[k]; c < D.col_start[k + 1]; c++) {
         const int n = D.col_nz[c], lt = D.ten_limidx[D.nz_tendon[n]];
         if (lt < 0) continue;
@@ -1213,25 +1326,31 @@ __device__ void constraintForce(const DevModel& D, const SmemLayout& L, float* s
           if (r >= 0) acc += EFC(E_COEF, r) * EFC(E_FORCE, r) * sm[L.tenJ + n];
         }
       }
+    #pragma unroll 1
     for (int b = 0; b < nb * ncon; b++) acc = fmaf(sm[L.conJ + b * nv + k], bf[b], acc);
     out[k] = acc;
   }
   __syncwarp();
 }
 // H = M + J^T D_active J (lower triangle), Cholesky in place
-__device__ void hessianFactor(const DevModel& D, const SmemLayout& L, float* sm, int lane, int ncon, int nefc) {
+__device__ __noinline__ void hessianFactor(int slot, float* sm, int lane, int ncon, int nefc) {
+  const DevModel& D = cP[slot].D; const SmemLayout& L = cP[slot].L;
   const int nv = D.nv, nb = D.maxbase;
   float* H = sm + L.H;
+  #pragma unroll 1
   for (int i = lane; i < nv * nv; i += 32) H[i] = 0.f;
   __syncwarp();
+  #pragma unroll 1
   for (int e = lane; e < D.nM; e += 32) H[D.M_row[e] * nv + D.M_col[e]] = sm[L.qM + e];
   __syncwarp();
+  #pragma unroll 1
   for (int k = lane; k < nv; k += 32) {
     const int li = D.dof_limidx[k];
     if (li < 0) continue;
-    for (int s = 0; s < 2; s++) { const int r = __float_as_int(sm[L.limrow + 2 * li + s]); if (r >= 0 && rowActive(D, L, sm, r)) H[k * nv + k] += EFC(E_D, r); }
+    for (int s = 0; s < 2; s++) { const int r = __float_as_int(sm[L.limrow + 2 * li + s]); if (r >= 0 && rowActive(slot, sm, r)) H[k * nv + k] += EFC(E_D, r); }
   }
   __syncwarp();
+  #pragma unroll 1
   for (int e = 0; e < D.neq; e++) {
     const int d1 = D.eq_dof1[e], d2 = D.eq_dof2[e];
     const float Dr = EFC(E_D, e), c = EFC(E_COEF, e);
@@ -1240,12 +1359,14 @@ __device__ void hessianFactor(const DevModel& D, const SmemLayout& L, float* sm,
     if (lane == 2 && d2 >= 0) H[d2 * nv + d2] += Dr * c * c;
     __syncwarp();
   }
+  #pragma unroll 1
   for (int lt = 0; lt < D.nlimt; lt++)
     for (int s = 0; s < 2; s++) {
       const int r = __float_as_int(sm[L.limrow + 2 * (D.nlimj + lt) + s]);
-      if (r < 0 || !rowActive(D, L, sm, r)) continue;
+      if (r < 0 || !rowActive(slot, sm, r)) continue;
       const int t = D.limt_ten[lt], n0 = D.ten_nzstart[t], cnt = D.ten_nzstart[t + 1] - n0;
       const float Dr = EFC(E_D, r);
+      #pragma unroll 1
       for (int i = lane; i < cnt * cnt; i += 32) {
         const int a = i / cnt, b = i - a * cnt;
         const int da = D.nz_dof[n0 + a], db = D.nz_dof[n0 + b];
@@ -1253,26 +1374,30 @@ __device__ void hessianFactor(const DevModel& D, const SmemLayout& L, float* sm,
       }
       __syncwarp();
     }
+  #pragma unroll 1
   for (int c = 0; c < ncon; c++) {
     const float* cr = sm + L.con + 12 * c;
     const int adr = __float_as_int(cr[8]), dim = __float_as_int(cr[9]);
     if (adr < 0) continue;
     // weights in base-row space: W = sum_p D_p w_p w_p^T, w_p = e_n +- mu e_t
     float Wnn = 0.f, Wnt[3] = {0.f, 0.f, 0.f}, Wtt[3] = {0.f, 0.f, 0.f};
-    if (dim == 1) { if (rowActive(D, L, sm, adr)) Wnn = EFC(E_D, adr); }
+    if (dim == 1) { if (rowActive(slot, sm, adr)) Wnn = EFC(E_D, adr); }
     else
+      #pragma unroll 1
       for (int k = 1; k < dim; k++) {
         const int r0 = adr + 2 * (k - 1);
         const float mu = EFC(E_COEF, r0);
-        const float Dp = rowActive(D, L, sm, r0) ? EFC(E_D, r0) : 0.f, Dm = rowActive(D, L, sm, r0 + 1) ? EFC(E_D, r0 + 1) : 0.f;
+        const float Dp = rowActive(slot, sm, r0) ? EFC(E_D, r0) : 0.f, Dm = rowActive(slot, sm, r0 + 1) ? EFC(E_D, r0 + 1) : 0.f;
         Wnn += Dp + Dm; Wnt[k - 1] = mu * (Dp - Dm); Wtt[k - 1] = mu * mu * (Dp + Dm);
       }
     if (Wnn == 0.f) continue;
     const float* Jn = sm + L.conJ + (c * nb) * nv;
+    #pragma unroll 1
     for (int i = lane; i < nv * nv; i += 32) {
       const int r = i / nv, cc = i - r * nv;
       if (cc > r) continue;
       float acc = Wnn * Jn[r] * Jn[cc];
+      #pragma unroll 1
       for (int k = 1; k < dim; k++) {
         const float* Jt = Jn + k * nv;
         acc += Wnt[k - 1] * (Jn[r] * Jt[cc] + Jt[r] * Jn[cc]) + Wtt[k - 1] * Jt[r] * Jt[cc];
@@ -1282,40 +1407,51 @@ __device__ void hessianFactor(const DevModel& D, const SmemLayout& L, float* sm,
     __syncwarp();
   }
   // left-looking Cholesky, lanes over rows
+  #pragma unroll 1
   for (int j = 0; j < nv; j++) {
     float sj = 0.f;
+    #pragma unroll 1
     for (int r = j + lane; r < nv; r += 32) {
       float s = H[r * nv + j];
+      #pragma unroll 1
       for (int k = 0; k < j; k++) s = fmaf(-H[r * nv + k], H[j * nv + k], s);
       if (r == j) sj = s; else H[r * nv + j] = s;
     }
     sj = __shfl_sync(FULLMASK, sj, 0);
     const float d = sqrtf(fmaxf(sj, MINVAL)), inv = 1.f / d;
     __syncwarp();
+    #pragma unroll 1
     for (int r = j + lane; r < nv; r += 32) { if (r == j) H[j * nv + j] = d; else H[r * nv + j] *= inv; }
     __syncwarp();
   }
 }
-__device__ void cholSolve(const DevModel& D, const float* H, float* x, int lane) {
+__device__ __noinline__ void cholSolve(int slot, const float* H, float* x, int lane) {
+  const DevModel& D = cP[slot].D;
   const int nv = D.nv;
+  #pragma unroll 1
   for (int j = 0; j < nv; j++) {
     const float xj = x[j] / H[j * nv + j];
     __syncwarp();
     if (lane == 0) x[j] = xj;
+    #pragma unroll 1
     for (int r = j + 1 + lane; r < nv; r += 32) x[r] = fmaf(-H[r * nv + j], xj, x[r]);
     __syncwarp();
   }
+  #pragma unroll 1
   for (int j = nv - 1; j >= 0; j--) {
     const float xj = x[j] / H[j * nv + j];
     __syncwarp();
     if (lane == 0) x[j] = xj;
+    #pragma unroll 1
     for (int r = lane; r < j; r += 32) x[r] = fmaf(-H[j * nv + r], xj, x[r]);
     __syncwarp();
   }
 }
 struct LsPt { float alpha, cost, d0, d1; };
-__device__ __forceinline__ LsPt lsEval(const DevModel& D, const SmemLayout& L, const float* sm, int lane, int nefc, float a, const float* qg) {
+__device__ __noinline__ LsPt lsEval(int slot, const float* sm, int lane, int nefc, float a, const float* qg) {
+  const DevModel& D = cP[slot].D; const SmemLayout& L = cP[slot].L;
   float q0 = 0.f, q1 = 0.f, q2 = 0.f;
+  #pragma unroll 1
   for (int r = lane; r < nefc; r += 32) {
     const float jar = EFC(E_JAR, r), jv = EFC(E_JV, r), x = jar + a * jv;
     if (((EFCI(E_DESC0, r) & 3) == ROW_EQ) || x < 0.f) {
@@ -1328,62 +1464,80 @@ __device__ __forceinline__ LsPt lsEval(const DevModel& D, const SmemLayout& L, c
   if (p.d1 <= 0.f) p.d1 = MINVAL;
   return p;
 }
-__device__ int solveNewton(const DevModel& D, const SmemLayout& L, float* sm, int lane, int ncon, int nefc, int* status) {
+__device__ __noinline__ int solveNewton(int slot, float* sm, int lane, int ncon, int nefc, int* status) {
+  const DevModel& D = cP[slot].D; const SmemLayout& L = cP[slot].L;
+  // Called by every warp of the CTA (nefc == 0: nothing to solve, the warp only takes part in the votes that keep
+  // the CTA's warps inside the same code).
   const int nv = D.nv;
+  bool active = nefc > 0;
   float* qacc = sm + L.qacc; float* Ma = sm + L.nvec; float* grad = Ma + nv; float* search = grad + nv; float* Mv = search + nv;
   float* tmp = Mv + nv;
   const float* smooth = sm + L.smooth; const float* qas = sm + L.qacc_smooth;
+  float gauss = 0.f, cost = 0.f;
+  const float scale = 1.f / (D.meaninertia * (float)max(1, nv));
+  if (active) {
   // warm start: cheaper of qacc_warmstart and qacc_smooth
   float costW = 3.4e38f;
   if (!(D.disableflags & DSBL_WARMSTART)) {
-    mulMsparse(D, sm + L.qM, sm + L.warm, Ma, lane);
+    mulMsparse(slot, sm + L.qM, sm + L.warm, Ma, lane);
     __syncwarp();
     float g = 0.f;
+    #pragma unroll 1
     for (int k = lane; k < nv; k += 32) g += 0.5f * (Ma[k] - smooth[k]) * (sm[L.warm + k] - qas[k]);
-    costW = warpSum(g) + residualCost(D, L, sm, lane, ncon, nefc, sm + L.warm);
+    costW = warpSum(g) + residualCost(slot, sm, lane, ncon, nefc, sm + L.warm);
   }
-  const float costS = residualCost(D, L, sm, lane, ncon, nefc, qas);
+  const float costS = residualCost(slot, sm, lane, ncon, nefc, qas);
   const bool useWarm = !(costW > costS);
+  #pragma unroll 1
   for (int k = lane; k < nv; k += 32) qacc[k] = useWarm ? sm[L.warm + k] : qas[k];
   __syncwarp();
-  mulMsparse(D, sm + L.qM, qacc, Ma, lane);
+  mulMsparse(slot, sm + L.qM, qacc, Ma, lane);
   __syncwarp();
-  float gauss = 0.f;
+  #pragma unroll 1
   for (int k = lane; k < nv; k += 32) gauss += 0.5f * (Ma[k] - smooth[k]) * (qacc[k] - qas[k]);
   gauss = warpSum(gauss);
-  float cost = gauss + residualCost(D, L, sm, lane, ncon, nefc, qacc);
-  const float scale = 1.f / (D.meaninertia * (float)max(1, nv));
+  cost = gauss + residualCost(slot, sm, lane, ncon, nefc, qacc);
+  }
   int iter = 0;
+  #pragma unroll 1
   for (;;) {
-    // gradient, Hessian, Newton direction
-    constraintForce(D, L, sm, lane, ncon, nefc, tmp);
-    float gn = 0.f;
-    for (int k = lane; k < nv; k += 32) { const float g = Ma[k] - smooth[k] - tmp[k]; grad[k] = g; search[k] = g; gn += g * g; }
-    gn = sqrtf(warpSum(gn));
-    if (iter > 0 && scale * gn < D.tolerance) break;
-    if (iter >= D.iterations) { *status |= MYO_WORLD_SOLVER_MAXITER; break; }
-    __syncwarp();
-    hessianFactor(D, L, sm, lane, ncon, nefc);
-    cholSolve(D, sm + L.H, search, lane);
+    // gradient and termination tests
+    if (active) {
+      constraintForce(slot, sm, lane, ncon, nefc, tmp);
+      float gn = 0.f;
+      #pragma unroll 1
+      for (int k = lane; k < nv; k += 32) { const float g = Ma[k] - smooth[k] - tmp[k]; grad[k] = g; search[k] = g; gn += g * g; }
+      gn = sqrtf(warpSum(gn));
+      if (iter > 0 && scale * gn < D.tolerance) active = false;
+      else if (iter >= D.iterations) { *status |= MYO_WORLD_SOLVER_MAXITER; active = false; }
+      __syncwarp();
+    }
+    if (!__syncthreads_or(active)) break;
+    if (active) do {
+    hessianFactor(slot, sm, lane, ncon, nefc);
+    cholSolve(slot, sm + L.H, search, lane);
     float sn = 0.f;
+    #pragma unroll 1
     for (int k = lane; k < nv; k += 32) { const float s = -search[k]; search[k] = s; sn += s * s; }
     sn = sqrtf(warpSum(sn));
     __syncwarp();
-    if (sn < MINVAL) break;
+    if (sn < MINVAL) { active = false; break; }
     // exact line search along `search`
-    mulMsparse(D, sm + L.qM, search, Mv, lane);
+    mulMsparse(slot, sm + L.qM, search, Mv, lane);
     float* bx = sm + L.basev;
-    baseMul(D, L, sm, lane, ncon, search, bx);
+    baseMul(slot, sm, lane, ncon, search, bx);
     __syncwarp();
-    for (int r = lane; r < nefc; r += 32) EFC(E_JV, r) = rowMul(D, L, sm, r, search, bx);
+    #pragma unroll 1
+    for (int r = lane; r < nefc; r += 32) EFC(E_JV, r) = rowMul(slot, sm, r, search, bx);
     float g1 = 0.f, g2 = 0.f;
+    #pragma unroll 1
     for (int k = lane; k < nv; k += 32) { g1 += search[k] * (Ma[k] - smooth[k]); g2 += 0.5f * search[k] * Mv[k]; }
     __syncwarp();
     const float qg[3] = {gauss, warpSum(g1), warpSum(g2)};
     const float gtol = D.tolerance * D.ls_tolerance * sn / scale;
     int lsiter = 0;
-    LsPt p0 = lsEval(D, L, sm, lane, nefc, 0.f, qg); lsiter++;
-    LsPt p1 = lsEval(D, L, sm, lane, nefc, p0.alpha - p0.d0 / p0.d1, qg); lsiter++;
+    LsPt p0 = lsEval(slot, sm, lane, nefc, 0.f, qg); lsiter++;
+    LsPt p1 = lsEval(slot, sm, lane, nefc, p0.alpha - p0.d0 / p0.d1, qg); lsiter++;
     if (p0.cost < p1.cost) p1 = p0;
     bool done = fabsf(p1.d0) < gtol;
     if (!done) {
@@ -1391,7 +1545,7 @@ __device__ int solveNewton(const DevModel& D, const SmemLayout& L, float* sm, in
       LsPt p2 = p1; bool have2 = false;
       while (p1.d0 * dir <= -gtol && lsiter < D.ls_iterations) {
         p2 = p1; have2 = true;
-        p1 = lsEval(D, L, sm, lane, nefc, p1.alpha - p1.d0 / p1.d1, qg); lsiter++;
+        p1 = lsEval(slot, sm, lane, nefc, p1.alpha - p1.d0 / p1.d1, qg); lsiter++;
         if (fabsf(p1.d0) < gtol) { done = true; break; }
       }
       if (!done && lsiter < D.ls_iterations && have2) {
@@ -1402,7 +1556,7 @@ __device__ int solveNewton(const DevModel& D, const SmemLayout& L, float* sm, in
           const float ca[3] = {lo.alpha - lo.d0 / lo.d1, hi.alpha - hi.d0 / hi.d1, 0.5f * (lo.alpha + hi.alpha)};
           LsPt cand[3];
 #pragma unroll
-          for (int q = 0; q < 3; q++) { cand[q] = lsEval(D, L, sm, lane, nefc, ca[q], qg); lsiter++; }
+          for (int q = 0; q < 3; q++) { cand[q] = lsEval(slot, sm, lane, nefc, ca[q], qg); lsiter++; }
 #pragma unroll
           for (int q = 0; q < 3; q++) {
             if (done) break;
@@ -1420,9 +1574,11 @@ __device__ int solveNewton(const DevModel& D, const SmemLayout& L, float* sm, in
       }
     }
     const float alpha = p1.alpha;
-    if (alpha == 0.f) break;
+    if (alpha == 0.f) { active = false; break; }
+    #pragma unroll 1
     for (int k = lane; k < nv; k += 32) { qacc[k] = fmaf(alpha, search[k], qacc[k]); Ma[k] = fmaf(alpha, Mv[k], Ma[k]); }
     float c2 = 0.f;
+    #pragma unroll 1
     for (int r = lane; r < nefc; r += 32) {
       const float jar = EFC(E_JAR, r) + alpha * EFC(E_JV, r);
       EFC(E_JAR, r) = jar;
@@ -1430,25 +1586,25 @@ __device__ int solveNewton(const DevModel& D, const SmemLayout& L, float* sm, in
     }
     __syncwarp();
     float g = 0.f;
+    #pragma unroll 1
     for (int k = lane; k < nv; k += 32) g += 0.5f * (Ma[k] - smooth[k]) * (qacc[k] - qas[k]);
     gauss = warpSum(g);
     const float newcost = gauss + warpSum(c2);
     iter++;
     const float improvement = scale * (cost - newcost);
     cost = newcost;
-    if (improvement < D.tolerance) {
-      constraintForce(D, L, sm, lane, ncon, nefc, tmp);
-      break;
-    }
+    if (improvement < D.tolerance) active = false;
+    } while (0);
+    __syncthreads();
   }
-  // tmp holds J^T f for the final jar in every exit path below except the early sn/alpha breaks: recompute to be safe
-  constraintForce(D, L, sm, lane, ncon, nefc, sm + L.qfrc_con);
+  if (nefc > 0) constraintForce(slot, sm, lane, ncon, nefc, sm + L.qfrc_con);
   return iter;
 }
 
 // ------------------------------------------------------------------------------------------ contact / efc outputs
-__device__ void writeConstraintOutputs(const DevModel& D, const SmemLayout& L, const FieldPtrs& F, float* sm, int lane, size_t w, int ncon,
+__device__ __noinline__ void writeConstraintOutputs(int slot, int fslot, float* sm, int lane, size_t w, int ncon,
                                        int nefc, int niter) {
+  const DevModel& D = cP[slot].D; const SmemLayout& L = cP[slot].L; const FieldPtrs& F = cP[fslot].F;
   const int nv = D.nv, ncm = D.nconmax, njm = D.njmax, nb = D.maxbase;
   int* ip;
   if (lane == 0) {
@@ -1456,6 +1612,7 @@ __device__ void writeConstraintOutputs(const DevModel& D, const SmemLayout& L, c
     if ((ip = (int*)F.p[MYO_F_NEFC])) ip[w] = nefc;
     if ((ip = (int*)F.p[MYO_F_SOLVER_NITER])) ip[w] = niter;
   }
+  #pragma unroll 1
   for (int c = lane; c < ncm; c += 32) {
     const bool on = c < ncon;
     const float* cr = sm + L.con + 12 * c;
@@ -1479,6 +1636,7 @@ __device__ void writeConstraintOutputs(const DevModel& D, const SmemLayout& L, c
     if ((o = (float*)F.p[MYO_F_CONTACT_SOLREF])) for (int k = 0; k < 2; k++) o[(w * ncm + c) * 2 + k] = on ? pp[7 + k] : 0.f;
     if ((o = (float*)F.p[MYO_F_CONTACT_SOLIMP])) for (int k = 0; k < 5; k++) o[(w * ncm + c) * 5 + k] = on ? pp[9 + k] : 0.f;
   }
+  #pragma unroll 1
   for (int r = lane; r < njm; r += 32) {
     const bool on = r < nefc;
     float* o;
@@ -1499,6 +1657,7 @@ __device__ void writeConstraintOutputs(const DevModel& D, const SmemLayout& L, c
   float* J = (float*)F.p[MYO_F_EFC_J];
   if (J) {
     const size_t n = (size_t)njm * nv;
+    #pragma unroll 1
     for (int i = lane; i < (int)n; i += 32) {
       const int r = i / nv, k = i - r * nv;
       float v = 0.f;
@@ -1516,137 +1675,167 @@ __device__ void writeConstraintOutputs(const DevModel& D, const SmemLayout& L, c
   (void)nb;
 }
 
-__constant__ FieldPtrs kNoFields;  // all NULL: substeps before the last one materialise nothing
 
-__device__ __forceinline__ bool warpAnyBad(const float* v, int n, int lane) {
+__device__ __noinline__ bool warpAnyBad(const float* v, int n, int lane) {
   bool bad = false;
+  #pragma unroll 1
   for (int i = lane; i < n; i += 32) bad |= !(fabsf(v[i]) < 1e10f);
   return __any_sync(FULLMASK, bad);
 }
-__device__ void resetState(const DevModel& D, const SmemLayout& L, float* sm, int lane) {
+__device__ __noinline__ void resetState(int slot, float* sm, int lane) {
+  const DevModel& D = cP[slot].D; const SmemLayout& L = cP[slot].L;
+  #pragma unroll 1
   for (int i = lane; i < D.nq; i += 32) sm[L.qpos + i] = D.qpos0[i];
+  #pragma unroll 1
   for (int i = lane; i < D.nv; i += 32) { sm[L.qvel + i] = 0.f; sm[L.warm + i] = 0.f; }
+  #pragma unroll 1
   for (int i = lane; i < D.na; i += 32) sm[L.act + i] = 0.f;
   __syncwarp();
 }
 
+// One CTA = WARPS worlds (one warp each).  The warps of a CTA move through the phases of the step together
+// (__syncthreads between phases, a CTA-wide vote inside the Newton loop): the step is ~300 KB of SASS, far beyond
+// the instruction caches, so keeping every warp of an SM inside the same few KB of code is what makes it run.
 template <int WARPS>
-__global__ void __launch_bounds__(32 * WARPS) stepKernel(const DevModel D, const SmemLayout L, const FieldPtrs F, int nworld, int nsub,
-                                                         int forward_only, const int* __restrict__ mask, int do_reset) {
+__global__ void __launch_bounds__(32 * WARPS) stepKernel(int slot, int nworld, int nsub, int forward_only,
+                                                         const int* __restrict__ mask, int do_reset) {
   extern __shared__ float smem[];
+  const DevModel& D = cP[slot].D; const SmemLayout& L = cP[slot].L; const FieldPtrs& F = cP[slot].F;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const size_t w = (size_t)blockIdx.x * WARPS + warp;
-  if (w >= (size_t)nworld) return;
-  if (do_reset && mask && !mask[w]) return;
+  const bool live = w < (size_t)nworld && !(do_reset && mask && !mask[w]);
   float* sm = smem + (size_t)warp * L.total;
   const int nq = D.nq, nv = D.nv, na = D.na, nu = D.nu;
   float* gq = (float*)F.p[MYO_F_QPOS] + w * nq; float* gv = (float*)F.p[MYO_F_QVEL] + w * nv;
   float* ga = (float*)F.p[MYO_F_ACT] + w * na; const float* gc = (const float*)F.p[MYO_F_CTRL] + w * nu;
   float* gw = (float*)F.p[MYO_F_QACC_WARMSTART] + w * nv; float* gt = (float*)F.p[MYO_F_TIME] + w;
   int* gs = (int*)F.p[MYO_F_STATUS];
-  int status = gs ? gs[w] : 0;
-  float time = *gt;
-  if (do_reset) {
-    resetState(D, L, sm, lane);
-    for (int i = lane; i < nu; i += 32) sm[L.ctrl + i] = 0.f;
-    time = 0.f; status = 0;
-  } else {
-    for (int i = lane; i < nq; i += 32) sm[L.qpos + i] = gq[i];
-    for (int i = lane; i < nv; i += 32) { sm[L.qvel + i] = gv[i]; sm[L.warm + i] = gw[i]; }
-    for (int i = lane; i < na; i += 32) sm[L.act + i] = ga[i];
-    for (int i = lane; i < nu; i += 32) sm[L.ctrl + i] = gc[i];
+  int status = 0;
+  float time = 0.f;
+  if (live) {
+    status = gs ? gs[w] : 0;
+    time = *gt;
+    if (do_reset) {
+      resetState(slot, sm, lane);
+      for (int i = lane; i < nu; i += 32) sm[L.ctrl + i] = 0.f;
+      time = 0.f; status = 0;
+    } else {
+      for (int i = lane; i < nq; i += 32) sm[L.qpos + i] = gq[i];
+      for (int i = lane; i < nv; i += 32) { sm[L.qvel + i] = gv[i]; sm[L.warm + i] = gw[i]; }
+      for (int i = lane; i < na; i += 32) sm[L.act + i] = ga[i];
+      for (int i = lane; i < nu; i += 32) sm[L.ctrl + i] = gc[i];
+    }
   }
-  __syncwarp();
+  __syncthreads();
   const int nloop = forward_only ? 1 : nsub;
   for (int sub = 0; sub < nloop; sub++) {
     const bool last = sub == nloop - 1;
-    const FieldPtrs& Fo = last ? F : kNoFields;
-    if (!forward_only) {   // mj_checkPos / mj_checkVel
-      if (warpAnyBad(sm + L.qpos, nq, lane)) { resetState(D, L, sm, lane); status |= MYO_WORLD_BADQPOS; }
-      if (warpAnyBad(sm + L.qvel, nv, lane)) { resetState(D, L, sm, lane); status |= MYO_WORLD_BADQVEL; }
+    const int fslot = last ? slot : MYO_NSLOT;
+    if (live && !forward_only) {   // mj_checkPos / mj_checkVel
+      if (warpAnyBad(sm + L.qpos, nq, lane)) { resetState(slot, sm, lane); status |= MYO_WORLD_BADQPOS; }
+      if (warpAnyBad(sm + L.qvel, nv, lane)) { resetState(slot, sm, lane); status |= MYO_WORLD_BADQVEL; }
     }
     int ncon = 0, nefc = 0, niter = 0;
+    bool redo = false;   // mj_checkAcc: a world whose qacc went bad is reset and its forward pass repeated
     for (int attempt = 0; attempt < 2; attempt++) {
-      kinematics(D, L, sm, lane);
-      comPos(D, L, sm, lane);
-      if (last) writePositionOutputs(D, L, Fo, sm, lane, w);
-      tendons(D, L, Fo, sm, lane, w);
-      inertia(D, L, Fo, sm, lane, w);
-      __syncwarp();
-      ncon = (D.disableflags & (DSBL_CONTACT | DSBL_CONSTRAINT)) ? 0 : collision(D, L, sm, lane, &status);
-      velocity(D, L, Fo, sm, lane, w);
-      actuation(D, L, Fo, sm, lane, w);
-      __syncwarp();
-      nefc = makeConstraint(D, L, sm, lane, ncon, &status);
-      niter = 0;
-      if (nefc == 0) {
+      const bool run = live && (attempt == 0 || redo);
+      if (run) { kinematics(slot, sm, lane); comPos(slot, sm, lane); }
+      __syncthreads();
+      if (run && last) writePositionOutputs(slot, fslot, sm, lane, w);
+      __syncthreads();
+      if (run) tendons(slot, fslot, sm, lane, w);
+      __syncthreads();
+      if (run) inertia(slot, fslot, sm, lane, w);
+      __syncthreads();
+      if (run) ncon = (D.disableflags & (DSBL_CONTACT | DSBL_CONSTRAINT)) ? 0 : collision(slot, sm, lane, &status);
+      __syncthreads();
+      if (run) velocity(slot, fslot, sm, lane, w);
+      __syncthreads();
+      if (run) actuation(slot, fslot, sm, lane, w);
+      __syncthreads();
+      if (run) nefc = makeConstraint(slot, sm, lane, ncon, &status);
+      __syncthreads();
+      if (run) niter = 0;
+      if (run && nefc == 0) {
         for (int i = lane; i < nv; i += 32) { const float a = sm[L.qacc_smooth + i]; sm[L.qacc + i] = a; sm[L.warm + i] = a; sm[L.qfrc_con + i] = 0.f; }
-      } else {
-        niter = solveNewton(D, L, sm, lane, ncon, nefc, &status);
+      }
+      const int it = solveNewton(slot, sm, lane, ncon, run ? nefc : 0, &status);
+      if (run && nefc > 0) {
+        niter = it;
         for (int i = lane; i < nv; i += 32) sm[L.warm + i] = sm[L.qacc + i];
       }
       __syncwarp();
-      if (forward_only || !warpAnyBad(sm + L.qacc, nv, lane)) break;
-      resetState(D, L, sm, lane);   // mj_checkAcc: reset and redo the forward pass
-      status |= MYO_WORLD_BADQACC;
+      redo = false;
+      if (run && !forward_only && warpAnyBad(sm + L.qacc, nv, lane)) {
+        resetState(slot, sm, lane);
+        status |= MYO_WORLD_BADQACC;
+        redo = true;
+      }
+      if (!__syncthreads_or(redo && attempt == 0)) break;
     }
-    if (last) {
-      writeConstraintOutputs(D, L, Fo, sm, lane, w, ncon, nefc, niter);
+    if (live && last) {
+      writeConstraintOutputs(slot, fslot, sm, lane, w, ncon, nefc, niter);
       float* o;
       if ((o = (float*)F.p[MYO_F_QACC])) for (int i = lane; i < nv; i += 32) o[w * nv + i] = sm[L.qacc + i];
       if ((o = (float*)F.p[MYO_F_QFRC_CONSTRAINT])) for (int i = lane; i < nv; i += 32) o[w * nv + i] = sm[L.qfrc_con + i];
       if ((o = (float*)F.p[MYO_F_QFRC_INVERSE])) for (int i = lane; i < nv; i += 32) o[w * nv + i] = 0.f;
     }
     if (forward_only) break;
-    // ---- mj_Euler with implicit joint damping
-    const float h = D.timestep;
-    float* qa = sm + L.tmpv;
-    if (D.any_damping) {
-      for (int e = lane; e < D.nM; e += 32) sm[L.qH + e] = sm[L.qM + e] + (D.M_row[e] == D.M_col[e] ? h * D.dof_damping[D.M_row[e]] : 0.f);
-      for (int i = lane; i < nv; i += 32) qa[i] = sm[L.smooth + i] + sm[L.qfrc_con + i];
-      __syncwarp();
-      factorLDL(D, sm + L.qH, sm + L.qHinv, lane);
-      solveLDL(D, sm + L.qH, sm + L.qHinv, qa, lane);
-    } else {
-      for (int i = lane; i < nv; i += 32) qa[i] = sm[L.qacc + i];
-      __syncwarp();
-    }
-    if (!(D.disableflags & DSBL_ACTUATION))
-      for (int i = lane; i < nu; i += 32) {
-        const int aa = D.act_actadr[i];
-        if (aa < 0) continue;
-        float a = fmaf(h, sm[L.actdot + aa], sm[L.act + aa]);
-        if (D.act_flags[i] & ACT_ACTLIMITED) a = clipf(a, D.act_actrange[2 * i], D.act_actrange[2 * i + 1]);
-        sm[L.act + aa] = a;
+    __syncthreads();
+    if (live) {
+      // ---- mj_Euler with implicit joint damping
+      const float h = D.timestep;
+      float* qa = sm + L.tmpv;
+      if (D.any_damping) {
+        for (int e = lane; e < D.nM; e += 32) sm[L.qH + e] = sm[L.qM + e] + (D.M_row[e] == D.M_col[e] ? h * D.dof_damping[D.M_row[e]] : 0.f);
+        for (int i = lane; i < nv; i += 32) qa[i] = sm[L.smooth + i] + sm[L.qfrc_con + i];
+        __syncwarp();
+        factorLDL(slot, sm + L.qH, sm + L.qHinv, lane);
+        solveLDL(slot, sm + L.qH, sm + L.qHinv, qa, lane);
+      } else {
+        for (int i = lane; i < nv; i += 32) qa[i] = sm[L.qacc + i];
+        __syncwarp();
       }
-    for (int i = lane; i < nv; i += 32) sm[L.qvel + i] = fmaf(h, qa[i], sm[L.qvel + i]);
-    __syncwarp();
-    for (int j = lane; j < D.njnt; j += 32) {
-      const int qa_ = D.jnt_qposadr[j], da = D.jnt_dofadr[j];
-      if (D.jnt_type[j] == JNT_FREE) {
-        for (int k = 0; k < 3; k++) sm[L.qpos + qa_ + k] = fmaf(h, sm[L.qvel + da + k], sm[L.qpos + qa_ + k]);
-        const f3 wv = ld3(sm + L.qvel + da + 3);
-        const float ang = norm3(wv) * h;
-        if (ang > 0.f) {
-          const f3 ax = unit3(wv);
-          float sn, cs; sincosf(0.5f * ang, &sn, &cs);
-          f4 dq; dq.w = cs; dq.x = ax.x * sn; dq.y = ax.y * sn; dq.z = ax.z * sn;
-          st4(sm + L.qpos + qa_ + 3, qnormalize(qmul(ld4(sm + L.qpos + qa_ + 3), dq)));
+      if (!(D.disableflags & DSBL_ACTUATION))
+        for (int i = lane; i < nu; i += 32) {
+          const int aa = D.act_actadr[i];
+          if (aa < 0) continue;
+          float a = fmaf(h, sm[L.actdot + aa], sm[L.act + aa]);
+          if (D.act_flags[i] & ACT_ACTLIMITED) a = clipf(a, D.act_actrange[2 * i], D.act_actrange[2 * i + 1]);
+          sm[L.act + aa] = a;
         }
-      } else sm[L.qpos + qa_] = fmaf(h, sm[L.qvel + da], sm[L.qpos + qa_]);
+      for (int i = lane; i < nv; i += 32) sm[L.qvel + i] = fmaf(h, qa[i], sm[L.qvel + i]);
+      __syncwarp();
+      for (int j = lane; j < D.njnt; j += 32) {
+        const int qa_ = D.jnt_qposadr[j], da = D.jnt_dofadr[j];
+        if (D.jnt_type[j] == JNT_FREE) {
+          for (int k = 0; k < 3; k++) sm[L.qpos + qa_ + k] = fmaf(h, sm[L.qvel + da + k], sm[L.qpos + qa_ + k]);
+          const f3 wv = ld3(sm + L.qvel + da + 3);
+          const float ang = norm3(wv) * h;
+          if (ang > 0.f) {
+            const f3 ax = unit3(wv);
+            float sn, cs; sincos_(0.5f * ang, &sn, &cs);
+            f4 dq; dq.w = cs; dq.x = ax.x * sn; dq.y = ax.y * sn; dq.z = ax.z * sn;
+            st4(sm + L.qpos + qa_ + 3, qnormalize(qmul(ld4(sm + L.qpos + qa_ + 3), dq)));
+          }
+        } else sm[L.qpos + qa_] = fmaf(h, sm[L.qvel + da], sm[L.qpos + qa_]);
+      }
+      time += h;
+      __syncwarp();
     }
-    time += h;
-    __syncwarp();
+    __syncthreads();
   }
   // ---- state out
-  if (!forward_only || do_reset) {
-    for (int i = lane; i < nq; i += 32) gq[i] = sm[L.qpos + i];
-    for (int i = lane; i < nv; i += 32) gv[i] = sm[L.qvel + i];
-    for (int i = lane; i < na; i += 32) ga[i] = sm[L.act + i];
-    if (lane == 0) *gt = time;
+  if (live) {
+    if (!forward_only || do_reset) {
+      for (int i = lane; i < nq; i += 32) gq[i] = sm[L.qpos + i];
+      for (int i = lane; i < nv; i += 32) gv[i] = sm[L.qvel + i];
+      for (int i = lane; i < na; i += 32) ga[i] = sm[L.act + i];
+      if (lane == 0) *gt = time;
+    }
+    for (int i = lane; i < nv; i += 32) gw[i] = sm[L.warm + i];
+    if (gs && lane == 0) gs[w] = status;
   }
-  for (int i = lane; i < nv; i += 32) gw[i] = sm[L.warm + i];
-  if (gs && lane == 0) gs[w] = status;
 }
 
 int64_t g_launches = 0;
@@ -1655,10 +1844,19 @@ int64_t g_launches = 0;
 
 int myo_kernel_smem_bytes(const SmemLayout& L) { return L.total * (int)sizeof(float); }
 int64_t myo_launch_counter() { return g_launches; }
+int myo_param_slots() { return MYO_NSLOT; }
 
-int myo_launch_step(const DevModel& D, const SmemLayout& L, const FieldPtrs& F, int nworld, int nsub, int forward_only,
-                    const int* reset_mask, int do_reset, void* stream) {
-  constexpr int WARPS = 1;
+// uploads a batch's parameters into its constant-memory slot (stream ordered)
+int myo_upload_params(int slot, const DevModel& D, const SmemLayout& L, const FieldPtrs& F, void* stream) {
+  static Params staging[MYO_NSLOT];   // must outlive the async copy
+  if (slot < 0 || slot >= MYO_NSLOT) return -1;
+  Params& P = staging[slot];
+  P.D = D; P.L = L; P.F = F;
+  return cudaMemcpyToSymbolAsync(cP, &P, sizeof(Params), (size_t)slot * sizeof(Params), cudaMemcpyHostToDevice, (cudaStream_t)stream) == cudaSuccess ? 0 : -1;
+}
+
+template <int WARPS>
+static int launchT(int slot, const SmemLayout& L, int nworld, int nsub, int forward_only, const int* reset_mask, int do_reset, void* stream) {
   const size_t smem = (size_t)WARPS * L.total * sizeof(float);
   static size_t configured = 0;
   if (smem > configured) {
@@ -1666,7 +1864,33 @@ int myo_launch_step(const DevModel& D, const SmemLayout& L, const FieldPtrs& F, 
     configured = smem;
   }
   const int grid = (nworld + WARPS - 1) / WARPS;
-  stepKernel<WARPS><<<grid, 32 * WARPS, smem, (cudaStream_t)stream>>>(D, L, F, nworld, nsub, forward_only, reset_mask, do_reset);
+  stepKernel<WARPS><<<grid, 32 * WARPS, smem, (cudaStream_t)stream>>>(slot, nworld, nsub, forward_only, reset_mask, do_reset);
   g_launches++;
   return cudaPeekAtLastError() == cudaSuccess ? 0 : -1;
+}
+
+// worlds per CTA: as many one-warp arenas as fit one SM's shared memory (<= 16)
+int myo_pick_warps(const SmemLayout& L) {
+  const size_t per = (size_t)L.total * sizeof(float), budget = 227 * 1024 - 1024;
+  const int fit = (int)(budget / per);
+  if (fit >= 16) return 16;
+  if (fit >= 12) return 12;
+  if (fit >= 8) return 8;
+  if (fit >= 6) return 6;
+  if (fit >= 4) return 4;
+  if (fit >= 2) return 2;
+  return 1;
+}
+
+int myo_launch_step(int slot, const SmemLayout& L, int nworld, int nsub, int forward_only, const int* reset_mask, int do_reset,
+                    int warps, void* stream) {
+  switch (warps) {
+    case 16: return launchT<16>(slot, L, nworld, nsub, forward_only, reset_mask, do_reset, stream);
+    case 12: return launchT<12>(slot, L, nworld, nsub, forward_only, reset_mask, do_reset, stream);
+    case 8: return launchT<8>(slot, L, nworld, nsub, forward_only, reset_mask, do_reset, stream);
+    case 6: return launchT<6>(slot, L, nworld, nsub, forward_only, reset_mask, do_reset, stream);
+    case 4: return launchT<4>(slot, L, nworld, nsub, forward_only, reset_mask, do_reset, stream);
+    case 2: return launchT<2>(slot, L, nworld, nsub, forward_only, reset_mask, do_reset, stream);
+    default: return launchT<1>(slot, L, nworld, nsub, forward_only, reset_mask, do_reset, stream);
+  }
 }
