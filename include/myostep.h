@@ -213,6 +213,12 @@ int myo_reset(myo_batch *b, const int32_t *world_mask_dev, void *cuda_stream);
 int myo_step_host(myo_batch *b, int nsubsteps, const float *qpos, const float *qvel, const float *act,
                   const float *ctrl, float *qpos_out, float *qvel_out, float *act_out, void *cuda_stream);
 
+/* Known-answer hook for the device rotation helpers used by kinematics and free-joint integration (reference KATs:
+ * myosuite/tests/mjx/test_quat_math.py against myosuite/utils/quat_math.py:15 mulQuat, :160 quat2mat, :209 rotVecQuat).
+ * Device pointers: qa, qb [n,4] (w,x,y,z); prod [n,4] = qa*qb; mat [n,9] = quat2mat(normalise(qa));
+ * rotated [n,3] = mat * qb[1:4]. */
+int myo_kat_quat(int n, const float *qa, const float *qb, float *prod, float *mat, float *rotated, void *cuda_stream);
+
 /* number of kernels launched by this library since load (for bench.py's gpu_launches) */
 int64_t myo_launch_count(void);
 

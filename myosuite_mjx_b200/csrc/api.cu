@@ -223,4 +223,11 @@ int myo_step_host(myo_batch* b, int nsubsteps, const float* qpos, const float* q
   return MYO_OK;
 }
 
+int myo_kat_quat(int n, const float* qa, const float* qb, float* prod, float* mat, float* rotated, void* stream) {
+  if (n <= 0 || !qa || !qb || !prod || !mat || !rotated) return fail(MYO_ERR_ARG, "bad argument");
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return fail(MYO_ERR_CUDA, "no CUDA device: libmyostep has no CPU fallback");
+  return myo_launch_quat_kat(n, qa, qb, prod, mat, rotated, stream) == 0 ? MYO_OK : fail(MYO_ERR_CUDA, "kernel launch failed");
+}
+
 }  // extern "C"

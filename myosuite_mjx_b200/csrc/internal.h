@@ -19,5 +19,6 @@ int myo_pick_warps(const SmemLayout& L);
 int myo_launch_step(int slot, const SmemLayout& L, int nworld, int nsub, int forward_only, const int* reset_mask, int do_reset,
                     int warps, void* stream);
 int myo_kernel_smem_bytes(const SmemLayout& L);
+int myo_launch_quat_kat(int n, const float* qa, const float* qb, float* prod, float* mat, float* rotated, void* stream);
 
 #endif

@@ -868,84 +868,96 @@ __device__ __noinline__ void actuation(int slot, int fslot, float* sm, int lane,
 }
 
 // ------------------------------------------------------------------------------------------ collision
-struct Shape { int type; f3 pos; const float* mat; f3 size; float margin; };
-__device__ __noinline__ f3 supportPt(const Shape& s, f3 dir) {
-  const f3 d = mulMT(s.mat, dir);
-  f3 r = mk3(0.f, 0.f, 0.f);
+// The convex narrow phase (Minkowski portal refinement on B - A) runs in float64: its result is defined by an
+// iteration with a 1e-6 stopping rule, and in float32 the portal degenerates near convergence (contact points of
+// ellipsoids moved by millimetres).  Few pairs reach it per world and B200 runs FP64 at half the FP32 rate.
+struct d3 { double x, y, z; };
+__device__ __forceinline__ d3 mkd(double x, double y, double z) { d3 r; r.x = x; r.y = y; r.z = z; return r; }
+__device__ __forceinline__ d3 operator+(d3 a, d3 b) { return mkd(a.x + b.x, a.y + b.y, a.z + b.z); }
+__device__ __forceinline__ d3 operator-(d3 a, d3 b) { return mkd(a.x - b.x, a.y - b.y, a.z - b.z); }
+__device__ __forceinline__ d3 operator*(d3 a, double s) { return mkd(a.x * s, a.y * s, a.z * s); }
+__device__ __forceinline__ double dot(d3 a, d3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+__device__ __forceinline__ d3 cross(d3 a, d3 b) { return mkd(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x); }
+__device__ __forceinline__ double norm3(d3 a) { return sqrt(dot(a, a)); }
+__device__ __forceinline__ d3 unit3(d3 a) { const double n = norm3(a); return n < 1e-15 ? mkd(1.0, 0.0, 0.0) : a * (1.0 / n); }
+struct Shape { int type; d3 pos; const float* mat; d3 size; double margin; };
+__device__ __noinline__ d3 supportPt(const Shape& s, d3 dir) {
+  const float* R = s.mat;
+  const d3 d = mkd(R[0] * dir.x + R[3] * dir.y + R[6] * dir.z, R[1] * dir.x + R[4] * dir.y + R[7] * dir.z, R[2] * dir.x + R[5] * dir.y + R[8] * dir.z);
+  d3 r = mkd(0.0, 0.0, 0.0);
   switch (s.type) {
     case G_SPHERE: r = d * s.size.x; break;
-    case G_CAPSULE: r = d * s.size.x; r.z += d.z >= 0.f ? s.size.y : -s.size.y; break;
+    case G_CAPSULE: r = d * s.size.x; r.z += d.z >= 0.0 ? s.size.y : -s.size.y; break;
     case G_ELLIPSOID: {
-      const f3 t = mk3(s.size.x * s.size.x * d.x, s.size.y * s.size.y * d.y, s.size.z * s.size.z * d.z);
-      r = t * rsqrtf(fmaxf(1e-30f, t.x * d.x + t.y * d.y + t.z * d.z));
+      const d3 t = mkd(s.size.x * s.size.x * d.x, s.size.y * s.size.y * d.y, s.size.z * s.size.z * d.z);
+      r = t * (1.0 / sqrt(fmax(1e-30, t.x * d.x + t.y * d.y + t.z * d.z)));
     } break;
     case G_CYLINDER: {
-      const float n = sqrtf(d.x * d.x + d.y * d.y);
-      if (n > 1e-12f) { r.x = s.size.x * d.x / n; r.y = s.size.x * d.y / n; }
-      r.z = d.z >= 0.f ? s.size.y : -s.size.y;
+      const double n = sqrt(d.x * d.x + d.y * d.y);
+      if (n > 1e-12) { r.x = s.size.x * d.x / n; r.y = s.size.x * d.y / n; }
+      r.z = d.z >= 0.0 ? s.size.y : -s.size.y;
     } break;
-    case G_BOX: r = mk3(d.x >= 0.f ? s.size.x : -s.size.x, d.y >= 0.f ? s.size.y : -s.size.y, d.z >= 0.f ? s.size.z : -s.size.z); break;
+    case G_BOX: r = mkd(d.x >= 0.0 ? s.size.x : -s.size.x, d.y >= 0.0 ? s.size.y : -s.size.y, d.z >= 0.0 ? s.size.z : -s.size.z); break;
     default: break;
   }
-  return mulM(s.mat, r) + s.pos + dir * s.margin;
+  return mkd(R[0] * r.x + R[1] * r.y + R[2] * r.z, R[3] * r.x + R[4] * r.y + R[5] * r.z, R[6] * r.x + R[7] * r.y + R[8] * r.z) + s.pos + dir * s.margin;
 }
-struct Sup { f3 v, a, b; };
-__device__ __noinline__ Sup mprSup(const Shape& A, const Shape& B, f3 d) {
-  Sup s; s.a = supportPt(A, d * -1.f); s.b = supportPt(B, d); s.v = s.b - s.a; return s;
+struct Sup { d3 v, a, b; };
+__device__ __noinline__ Sup mprSup(const Shape& A, const Shape& B, d3 d) {
+  Sup s; s.a = supportPt(A, d * -1.0); s.b = supportPt(B, d); s.v = s.b - s.a; return s;
 }
-// Minkowski portal refinement on B - A (same statement as oracle/mjstep_oracle.cpp, float32)
-__device__ __noinline__ bool mprPenetration(const Shape& A, const Shape& B, float tol, int maxit, float* depth, f3* nrm, f3* pos) {
-  f3 v0 = B.pos - A.pos;
-  if (norm3(v0) < 1e-12f) v0 = mk3(1e-5f, 0.f, 0.f);
-  f3 dir = unit3(v0 * -1.f);
+__device__ __noinline__ bool mprPenetration(const Shape& A, const Shape& B, double tol, int maxit, double* depth, d3* nrm, d3* pos) {
+  d3 v0 = B.pos - A.pos;
+  if (norm3(v0) < 1e-12) v0 = mkd(1e-5, 0.0, 0.0);
+  d3 dir = unit3(v0 * -1.0);
   Sup s1 = mprSup(A, B, dir);
-  if (dot(s1.v, dir) <= 0.f) return false;
+  if (dot(s1.v, dir) <= 0.0) return false;
   dir = cross(s1.v, v0);
-  if (norm3(dir) < 1e-7f * fmaxf(1e-20f, norm3(s1.v) * norm3(v0))) {
-    const f3 n = unit3(s1.v - v0);
-    *depth = dot(s1.v, n); *nrm = n * -1.f; *pos = (s1.a + s1.b) * 0.5f;
+  if (norm3(dir) < 1e-12 * fmax(1.0, norm3(s1.v) * norm3(v0))) {
+    const d3 n = unit3(s1.v - v0);
+    *depth = dot(s1.v, n); *nrm = n * -1.0; *pos = (s1.a + s1.b) * 0.5;
     return true;
   }
   dir = unit3(dir);
   Sup s2 = mprSup(A, B, dir);
-  if (dot(s2.v, dir) <= 0.f) return false;
+  if (dot(s2.v, dir) <= 0.0) return false;
   dir = unit3(cross(s1.v - v0, s2.v - v0));
-  if (dot(dir, v0) > 0.f) { Sup t = s1; s1 = s2; s2 = t; dir = dir * -1.f; }
+  if (dot(dir, v0) > 0.0) { Sup t = s1; s1 = s2; s2 = t; dir = dir * -1.0; }
   Sup s3;
   #pragma unroll 1
   for (int it = 0;; it++) {
     if (it > maxit) return false;
     s3 = mprSup(A, B, dir);
-    if (dot(s3.v, dir) <= 0.f) return false;
-    if (dot(cross(s1.v, s3.v), v0) < 0.f) { s2 = s3; dir = unit3(cross(s1.v - v0, s3.v - v0)); continue; }
-    if (dot(cross(s3.v, s2.v), v0) < 0.f) { s1 = s3; dir = unit3(cross(s3.v - v0, s2.v - v0)); continue; }
+    if (dot(s3.v, dir) <= 0.0) return false;
+    if (dot(cross(s1.v, s3.v), v0) < 0.0) { s2 = s3; dir = unit3(cross(s1.v - v0, s3.v - v0)); continue; }
+    if (dot(cross(s3.v, s2.v), v0) < 0.0) { s1 = s3; dir = unit3(cross(s3.v - v0, s2.v - v0)); continue; }
     break;
   }
   bool hit = false;
   #pragma unroll 1
   for (int it = 0;; it++) {
     dir = unit3(cross(s2.v - s1.v, s3.v - s1.v));
-    if (dot(dir, s1.v) >= 0.f) hit = true;
+    if (dot(dir, s1.v) >= 0.0) hit = true;
     const Sup s4 = mprSup(A, B, dir);
-    if (dot(s4.v, dir) < 0.f && !hit) return false;
-    const float adv = fminf(fminf(dot(s4.v - s1.v, dir), dot(s4.v - s2.v, dir)), dot(s4.v - s3.v, dir));
+    if (dot(s4.v, dir) < 0.0 && !hit) return false;
+    const double adv = fmin(fmin(dot(s4.v - s1.v, dir), dot(s4.v - s2.v, dir)), dot(s4.v - s3.v, dir));
     if (adv <= tol || it >= maxit) {
       if (!hit) return false;
-      const float d = dot(dir, s1.v);
-      const f3 p = dir * d, e0 = s2.v - s1.v, e1 = s3.v - s1.v, e2 = p - s1.v;
-      const float d00 = dot(e0, e0), d01 = dot(e0, e1), d11 = dot(e1, e1), d20 = dot(e2, e0), d21 = dot(e2, e1);
-      const float den = d00 * d11 - d01 * d01;
-      float b1 = 1.f, b2 = 0.f, b3 = 0.f;
-      if (fabsf(den) > 1e-30f) { b2 = (d11 * d20 - d01 * d21) / den; b3 = (d00 * d21 - d01 * d20) / den; b1 = 1.f - b2 - b3; }
-      b1 = clipf(b1, 0.f, 1.f); b2 = clipf(b2, 0.f, 1.f); b3 = clipf(b3, 0.f, 1.f);
-      const float bs = 1.f / fmaxf(1e-30f, b1 + b2 + b3);
-      const f3 pa = (s1.a * b1 + s2.a * b2 + s3.a * b3) * bs, pb = (s1.b * b1 + s2.b * b2 + s3.b * b3) * bs;
-      *depth = d; *nrm = dir * -1.f; *pos = (pa + pb) * 0.5f;
+      const double d = dot(dir, s1.v);
+      const d3 p = dir * d, e0 = s2.v - s1.v, e1 = s3.v - s1.v, e2 = p - s1.v;
+      const double d00 = dot(e0, e0), d01 = dot(e0, e1), d11 = dot(e1, e1), d20 = dot(e2, e0), d21 = dot(e2, e1);
+      const double den = d00 * d11 - d01 * d01;
+      double b1 = 1.0, b2 = 0.0, b3 = 0.0;
+      if (fabs(den) > 1e-30) { b2 = (d11 * d20 - d01 * d21) / den; b3 = (d00 * d21 - d01 * d20) / den; b1 = 1.0 - b2 - b3; }
+      b1 = fmin(fmax(b1, 0.0), 1.0); b2 = fmin(fmax(b2, 0.0), 1.0); b3 = fmin(fmax(b3, 0.0), 1.0);
+      const double bs = 1.0 / fmax(1e-30, b1 + b2 + b3);
+      const d3 pa = (s1.a * b1 + s2.a * b2 + s3.a * b3) * bs, pb = (s1.b * b1 + s2.b * b2 + s3.b * b3) * bs;
+      *depth = d; *nrm = dir * -1.0; *pos = (pa + pb) * 0.5;
       return true;
     }
-    const f3 c = cross(s4.v, v0);
-    if (dot(s1.v, c) > 0.f) { if (dot(s2.v, c) > 0.f) s1 = s4; else s3 = s4; }
-    else { if (dot(s3.v, c) > 0.f) s2 = s4; else s1 = s4; }
+    const d3 c = cross(s4.v, v0);
+    if (dot(s1.v, c) > 0.0) { if (dot(s2.v, c) > 0.0) s1 = s4; else s3 = s4; }
+    else { if (dot(s3.v, c) > 0.0) s2 = s4; else s1 = s4; }
   }
 }
 struct Hit { float dist; f3 pos, nrm; };
@@ -978,9 +990,10 @@ __device__ __noinline__ int collidePair(int slot, const float* sm, int pr, Hit* 
         if (dist < margin) { h[n].dist = dist; h[n].pos = c - ax1 * (sz2.x + 0.5f * dist); h[n].nrm = ax1; n++; }
       }
     } else {
-      Shape s; s.type = t2; s.pos = p2; s.mat = R2; s.size = sz2; s.margin = 0.f;
-      const f3 sp = supportPt(s, ax1 * -1.f);
-      const float dist = dot(sp - p1, ax1);
+      Shape s; s.type = t2; s.pos = mkd(p2.x, p2.y, p2.z); s.mat = R2; s.size = mkd(sz2.x, sz2.y, sz2.z); s.margin = 0.0;
+      const d3 spd = supportPt(s, mkd(-ax1.x, -ax1.y, -ax1.z));
+      const f3 sp = mk3((float)spd.x, (float)spd.y, (float)spd.z);
+      const float dist = (float)((spd.x - p1.x) * ax1.x + (spd.y - p1.y) * ax1.y + (spd.z - p1.z) * ax1.z);
       if (dist < margin) { h[0].dist = dist; h[0].pos = sp - ax1 * (0.5f * dist); h[0].nrm = ax1; n = 1; }
     }
     return n;
@@ -1004,11 +1017,12 @@ __device__ __noinline__ int collidePair(int slot, const float* sm, int pr, Hit* 
     h[0] = sphereSphere(p1 + a1 * x1, sz1.x, p2 + a2 * x2, sz2.x);
   } else {
     Shape A, B;
-    A.type = t1; A.pos = p1; A.mat = R1; A.size = sz1; A.margin = 0.5f * margin;
-    B.type = t2; B.pos = p2; B.mat = R2; B.size = sz2; B.margin = 0.5f * margin;
-    float depth; f3 nrm, pos;
-    if (!mprPenetration(A, B, 1e-6f, 50, &depth, &nrm, &pos)) return 0;
-    h[0].dist = margin - depth; h[0].pos = pos; h[0].nrm = nrm;
+    A.type = t1; A.pos = mkd(p1.x, p1.y, p1.z); A.mat = R1; A.size = mkd(sz1.x, sz1.y, sz1.z); A.margin = 0.5 * (double)margin;
+    B.type = t2; B.pos = mkd(p2.x, p2.y, p2.z); B.mat = R2; B.size = mkd(sz2.x, sz2.y, sz2.z); B.margin = 0.5 * (double)margin;
+    double depth; d3 nrm, pos;
+    if (!mprPenetration(A, B, 1e-6, 50, &depth, &nrm, &pos)) return 0;
+    h[0].dist = (float)((double)margin - depth); h[0].pos = mk3((float)pos.x, (float)pos.y, (float)pos.z);
+    h[0].nrm = mk3((float)nrm.x, (float)nrm.y, (float)nrm.z);
   }
   return h[0].dist < margin ? 1 : 0;
 }
@@ -1838,9 +1852,27 @@ __global__ void __launch_bounds__(32 * WARPS) stepKernel(int slot, int nworld, i
   }
 }
 
+// known-answer hook for the rotation helpers above (tests/: reference KATs of myosuite/utils/quat_math.py)
+__global__ void quatKatKernel(int n, const float* __restrict__ qa, const float* __restrict__ qb, float* __restrict__ prod,
+                              float* __restrict__ mat, float* __restrict__ rotated) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const f4 a = ld4(qa + 4 * i), b = ld4(qb + 4 * i);
+  st4(prod + 4 * i, qmul(a, b));
+  float R[9]; q2m(R, qnormalize(a));
+  for (int k = 0; k < 9; k++) mat[9 * i + k] = R[k];
+  st3(rotated + 3 * i, mulM(R, mk3(b.x, b.y, b.z)));
+}
+
 int64_t g_launches = 0;
 
 }  // namespace
+
+int myo_launch_quat_kat(int n, const float* qa, const float* qb, float* prod, float* mat, float* rotated, void* stream) {
+  quatKatKernel<<<(n + 127) / 128, 128, 0, (cudaStream_t)stream>>>(n, qa, qb, prod, mat, rotated);
+  g_launches++;
+  return cudaPeekAtLastError() == cudaSuccess ? 0 : -1;
+}
 
 int myo_kernel_smem_bytes(const SmemLayout& L) { return L.total * (int)sizeof(float); }
 int64_t myo_launch_counter() { return g_launches; }

@@ -56,6 +56,7 @@ def lib():
         L.myo_step.argtypes = [vp, i32, vp]
         L.myo_reset.argtypes = [vp, vp, vp]
         L.myo_step_host.argtypes = [vp, i32] + [vp] * 8
+        L.myo_kat_quat.argtypes = [i32] + [vp] * 6
         _lib = L
     return _lib
 
@@ -67,4 +68,4 @@ def check(rc):
 
 EXPORTS = ["myo_model_create", "myo_model_destroy", "myo_batch_create", "myo_batch_destroy", "myo_batch_nconmax",
            "myo_batch_njmax", "myo_batch_smem_bytes", "myo_field_count", "myo_field_itemsize", "myo_field_is_int", "myo_field_name", "myo_batch_bind",
-           "myo_forward", "myo_step", "myo_reset", "myo_step_host", "myo_launch_count", "myo_last_error"]
+           "myo_forward", "myo_step", "myo_reset", "myo_step_host", "myo_launch_count", "myo_last_error", "myo_kat_quat"]

@@ -104,7 +104,7 @@ class Data:
 
     def __getattr__(self, name):
         t = self.__dict__.get("_t", {})
-        key = name.lower()
+        key = {"q": "qpos", "qd": "qvel"}.get(name, name.lower())   # brax State aliases (myodm_v0.py:201-202)
         if key in t:
             return self._view(key, t[key])
         raise AttributeError(name)

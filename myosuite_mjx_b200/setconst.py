@@ -4,7 +4,7 @@ through `mujoco.MjModel.from_xml_path`, myosuite/mjx/play.py:8).
 A small float64 numpy/python evaluation of the position stage at `qpos0` (kinematics, subtree COM, spatial
 tendons with wrapping, joint-space inertia) gives `tendon_length0`, `dof_invweight0`, `body_invweight0`,
 `tendon_invweight0`, `actuator_acc0` and `stat_meaninertia`.  Host side, runs once per model; it is part of
-the model compiler, not of the step path, and it is NOT the parity oracle (that lives in oracle/).
+the model compiler, not of the step path, and it is NOT the parity checker used by the tests.
 """
 from __future__ import annotations
 

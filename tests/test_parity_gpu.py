@@ -1,0 +1,225 @@
+"""Parity of the CUDA path (through the C ABI / mjx layer) with the CPU oracle on the same seeded inputs.
+
+Tolerances (float32 kernel vs float64 oracle), error measured relative to the field's own scale over the batch:
+  * position / velocity / actuation stage fields (no constraint solve involved): 1e-4
+  * integer fields (ncon, nefc, contact geom pairs, dims, efc types): bit-exact
+  * qacc / qfrc_constraint of worlds with active constraints: 2e-3 (iterative Newton solve in float32)
+  * one mj_step from synchronised states: qpos 1e-5 abs, qvel rel 1e-3, act / actuator_force rel 1e-4
+The oracle itself is a restatement of MuJoCo 3.2.8 semantics (PARITY UNPINNED, see oracle/mjstep_oracle.cpp)."""
+import numpy as np
+import pytest
+
+import parity
+
+pytestmark = pytest.mark.gpu
+
+STAGE_FIELDS = ["xpos", "xquat", "xmat", "xipos", "ximat", "xanchor", "xaxis", "geom_xpos", "geom_xmat", "site_xpos", "site_xmat",
+                "subtree_com", "cinert", "crb", "cdof", "cdof_dot", "cvel", "ten_length", "ten_velocity", "ten_J",
+                "actuator_length", "actuator_velocity", "actuator_moment", "actuator_force", "act_dot", "qM", "qLDiagInv",
+                "qfrc_bias", "qfrc_passive", "qfrc_spring", "qfrc_damper", "qfrc_actuator", "qfrc_smooth", "qacc_smooth"]
+MODELS = ["elbow", "hand", "hand_pose", "hand_sar", "legs"]
+
+
+@pytest.fixture(scope="module")
+def fwd(models):
+    cache = {}
+
+    def get(name, nw=32, seed=1234, spread=0.9):
+        key = (name, nw, seed, spread)
+        if key not in cache:
+            m = models(name)
+            qpos, qvel, act, ctrl = parity.random_state(m, nw, seed, qpos_spread=spread)
+            ref, ex = parity.oracle_forward(m, qpos, qvel, act, ctrl, parity.FLOAT_FIELDS)
+            model, d, got = parity.gpu_forward(m, qpos, qvel, act, ctrl, nconmax=32, njmax=160)
+            cache[key] = (m, ref, ex, got, d)
+        return cache[key]
+    return get
+
+
+@pytest.mark.parametrize("name", MODELS)
+def test_forward_stage_fields(fwd, name):
+    m, ref, ex, got, d = fwd(name)
+    rep = parity.field_errors(ref, got, STAGE_FIELDS)
+    bad = {k: v for k, v in rep.items() if v[1] > 1e-4}
+    assert not bad, f"{name}: fields beyond rel 1e-4: {bad}"
+
+
+@pytest.mark.parametrize("name", MODELS)
+def test_contact_and_row_indices_exact(fwd, name):
+    m, ref, ex, got, d = fwd(name)
+    nw = len(ex["ncon"])
+    assert np.array_equal(got.ncon[:, 0], np.array(ex["ncon"])), "ncon differs"
+    assert np.array_equal(got.nefc[:, 0], np.array(ex["nefc"])), "nefc differs"
+    assert not np.any(got.status & 6), "capacity overflow in the parity batch"
+    cg = got.contact_geom.reshape(nw, -1, 2)
+    for w in range(nw):
+        n = ex["ncon"][w]
+        assert np.array_equal(cg[w, :n], ex["contact_geom"][w]), f"world {w}: contact geom pairs differ"
+        assert np.all(cg[w, n:] == -1)
+    if max(ex["ncon"]) > 0:
+        # contact geometry from the closed-form / MPR narrow phase
+        for w in range(nw):
+            n = ex["ncon"][w]
+            if n:
+                np.testing.assert_allclose(got.contact_dist[w, :n], ex["contact_dist"][w], atol=2e-5)
+                np.testing.assert_allclose(got.contact_pos.reshape(nw, -1, 3)[w, :n], ex["contact_pos"][w], atol=2e-3)   # MPR pairs: iterative narrow phase in float32
+                np.testing.assert_allclose(got.contact_frame.reshape(nw, -1, 9)[w, :n, :3], ex["contact_frame"][w][:, :3], atol=2e-3)
+
+
+@pytest.mark.parametrize("name", MODELS)
+def test_constrained_acceleration(fwd, models, name):
+    """qacc after the Newton solve.  Worlds whose contacts come from the iterative convex narrow phase are sensitive
+    to float32 rounding of the contact point (tiny rotational inertia of the free object): the oracle's own float32
+    build is the yardstick -- a world counts as failed only if the CUDA path is off (> 2e-3 of the batch scale) while
+    the float32 oracle is not (< 5e-4)."""
+    m, ref, ex, got, d = fwd(name)
+    nw = len(ex["ncon"])
+    qpos, qvel, act, ctrl = parity.random_state(models(name), nw, 1234, qpos_spread=0.9)
+    reff, _ = parity.oracle_forward(models(name), qpos, qvel, act, ctrl, ["qacc"], use_float=True)
+    scale = max(np.abs(ref["qacc"]).max(), 1e-9)
+    e_gpu = np.abs(got.qacc - ref["qacc"]).max(axis=1) / scale
+    e_f32 = np.abs(reff["qacc"] - ref["qacc"]).max(axis=1) / scale
+    failed = (e_gpu > 2e-3) & (e_f32 < 5e-4)
+    assert failed.sum() <= max(1, nw // 16), f"{name}: worlds {np.nonzero(failed)[0]} gpu {e_gpu[failed]} f32 oracle {e_f32[failed]}"
+    assert np.median(e_gpu) < 5e-4
+    free = np.array(ex["nefc"]) == 0
+    if free.any():
+        assert e_gpu[free].max() <= 1e-4
+
+
+@pytest.mark.parametrize("name", MODELS)
+def test_single_step_from_synchronised_state(models, name):
+    import oracle
+    m = models(name)
+    nw = 16
+    qpos, qvel, act, ctrl = parity.random_state(m, nw, 77, qpos_spread=0.6)
+    model, d, got = parity.gpu_forward(m, qpos, qvel, act, ctrl, nconmax=32, njmax=160, step=1)
+    o = oracle.Oracle(m)
+    for w in range(nw):
+        o.reset(); o.set_state(qpos[w], qvel[w], act[w], ctrl[w]); o.step(1)
+        assert np.abs(got.qpos[w] - o.qpos).max() < 1e-5 + 1e-3 * m.opt_timestep * np.abs(o.qvel).max()
+        assert np.abs(got.qvel[w] - o.qvel).max() < 1e-3 * max(1.0, np.abs(o.qvel).max())
+        assert np.abs(got.act[w] - o.act).max() < 1e-4
+        assert abs(float(got.time[w, 0]) - float(o.time[0])) < 1e-7
+        sc = max(np.abs(o.actuator_force).max(), 1e-9)
+        assert np.abs(got.actuator_force[w] - o.actuator_force).max() < 1e-4 * sc
+
+
+@pytest.mark.parametrize("name", ["elbow", "legs"])
+def test_bounded_drift_1000_steps(models, name):
+    """Drift envelope over 1000 steps from rest with random held ctrl (contact-free / weakly chaotic configs)."""
+    import oracle
+    m = models(name)
+    nw = 8
+    qpos, qvel, act, ctrl = parity.random_state(m, nw, 5, qpos_spread=0.3)
+    model, d, got = parity.gpu_forward(m, qpos, 0 * qvel, 0 * act, ctrl, step=1000 if name == "elbow" else 200)
+    o = oracle.Oracle(m)
+    n = 1000 if name == "elbow" else 200
+    for w in range(4):
+        o.reset(); o.set_state(qpos[w], 0 * qvel[w], 0 * act[w], ctrl[w]); o.step(n)
+        assert np.abs(got.qpos[w] - o.qpos).max() < (1e-3 if name == "elbow" else 2e-2)
+        assert abs(float(got.time[w, 0]) - n * m.opt_timestep) < 1e-3
+    assert np.all(got.status == 0)
+
+
+def test_fused_substeps_equal_repeated_steps(models):
+    import torch
+    from myosuite_mjx_b200 import mjx
+    m = models("hand")
+    qpos, qvel, act, ctrl = parity.random_state(m, 64, 3, qpos_spread=0.5)
+    model = mjx.put_model(m)
+    a = mjx.put_data(model, dict(qpos=qpos, qvel=qvel, act=act, ctrl=ctrl), nworld=64, fields="core")
+    b = mjx.put_data(model, dict(qpos=qpos, qvel=qvel, act=act, ctrl=ctrl), nworld=64, fields="core")
+    mjx.step(model, a, 5)
+    for _ in range(5):
+        mjx.step(model, b, 1)
+    torch.cuda.synchronize()
+    for f in ("qpos", "qvel", "act", "time", "qacc_warmstart"):
+        assert torch.equal(getattr(a, f), getattr(b, f)), f"{f}: fused substeps differ from repeated launches"
+
+
+def test_deterministic_and_output_mask_invariant(models):
+    """Bitwise-identical state whether all of mjData or only the core fields are materialised, run twice."""
+    import torch
+    from myosuite_mjx_b200 import mjx
+    m = models("hand")
+    qpos, qvel, act, ctrl = parity.random_state(m, 96, 8, qpos_spread=0.5)
+    model = mjx.put_model(m)
+    outs = []
+    for fields in ("all", "core", "all"):
+        d = mjx.put_data(model, dict(qpos=qpos, qvel=qvel, act=act, ctrl=ctrl), nworld=96, fields=fields)
+        mjx.step(model, d, 3)
+        torch.cuda.synchronize()
+        outs.append((d.qpos.clone(), d.qvel.clone(), d.act.clone()))
+    for k in range(3):
+        assert torch.equal(outs[0][k], outs[1][k]) and torch.equal(outs[0][k], outs[2][k])
+
+
+def test_reset_and_masked_reset(models):
+    import torch
+    from myosuite_mjx_b200 import mjx
+    m = models("hand")
+    qpos, qvel, act, ctrl = parity.random_state(m, 32, 21)
+    model = mjx.put_model(m)
+    d = mjx.put_data(model, dict(qpos=qpos, qvel=qvel, act=act, ctrl=ctrl), nworld=32, fields="core")
+    mjx.step(model, d, 4)
+    before = d.qpos.clone()
+    mask = torch.zeros(32, dtype=torch.int32, device="cuda"); mask[::2] = 1
+    mjx.reset(model, d, mask)
+    torch.cuda.synchronize()
+    q0 = torch.as_tensor(np.asarray(m.qpos0, dtype=np.float32), device="cuda")
+    assert torch.equal(d.qpos[::2], q0.expand(16, -1)) and torch.equal(d.qpos[1::2], before[1::2])
+    assert float(d.qvel[::2].abs().max()) == 0 and float(d.act[::2].abs().max()) == 0 and float(d.time[::2].abs().max()) == 0
+    assert float(d.time[1::2].min()) > 0
+    mjx.reset(model, d)
+    torch.cuda.synchronize()
+    assert torch.equal(d.qpos, q0.expand(32, -1)) and int(d.status.abs().max()) == 0
+
+
+def test_bad_state_is_flagged_and_reset(models):
+    import torch
+    from myosuite_mjx_b200 import mjx
+    m = models("elbow")
+    model = mjx.put_model(m)
+    d = mjx.make_data(model, 8, fields="core")
+    d.qvel[3, 0] = float("nan")
+    mjx.step(model, d, 1)
+    torch.cuda.synchronize()
+    assert int(d.status[3, 0]) & 32 and torch.isfinite(d.qpos).all() and torch.isfinite(d.qvel).all()
+    assert int(d.status[0, 0]) == 0
+
+
+def test_bind_errors(models):
+    import ctypes
+    import torch
+    from myosuite_mjx_b200 import lib, mjx
+    m = models("elbow")
+    model = mjx.put_model(m)
+    d = mjx.make_data(model, 4, fields="core")
+    with pytest.raises(lib.MyoError):
+        d.bind("qpos", torch.zeros((4, 7), device="cuda"))          # wrong size
+    with pytest.raises(ValueError):
+        d.bind("qpos", torch.zeros((4, m.nq)))                      # host tensor
+    assert lib.lib().myo_batch_bind(d._h, 0, None, 0) == -1         # state fields cannot be unbound
+    with pytest.raises(lib.MyoError):
+        lib.check(lib.lib().myo_step(d._h, 0, None))
+
+
+def test_quat_kat_on_device():
+    """Device rotation helpers against the reference's numpy helpers (golden: tests/golden/quat_kat.npz,
+    rtol = atol = 1e-5 as in myosuite/tests/mjx/test_quat_math.py:619-625)."""
+    import ctypes
+    import os
+    import torch
+    from conftest import ROOT
+    from myosuite_mjx_b200 import lib
+    k = np.load(os.path.join(ROOT, "tests", "golden", "quat_kat.npz"))
+    n = len(k["qa"])
+    qa = torch.tensor(k["qa"], dtype=torch.float32, device="cuda"); qb = torch.tensor(k["qb"], dtype=torch.float32, device="cuda")
+    prod = torch.zeros((n, 4), device="cuda"); mat = torch.zeros((n, 9), device="cuda"); rot = torch.zeros((n, 3), device="cuda")
+    vp = ctypes.c_void_p
+    lib.check(lib.lib().myo_kat_quat(n, vp(qa.data_ptr()), vp(qb.data_ptr()), vp(prod.data_ptr()), vp(mat.data_ptr()), vp(rot.data_ptr()), None))
+    torch.cuda.synchronize()
+    np.testing.assert_allclose(prod.cpu().numpy(), k["mul"], rtol=1e-5, atol=1e-5)
+    np.testing.assert_allclose(mat.cpu().numpy(), k["mat"], rtol=1e-5, atol=1e-5)
+    np.testing.assert_allclose(rot.cpu().numpy(), k["rot"], rtol=1e-5, atol=1e-5)
