@@ -47,6 +47,9 @@ P3 add(P3 a, P3 b) { return {a.x + b.x, a.y + b.y, a.z + b.z}; }
 template <typename T> T* upload(const std::vector<T>& v, std::vector<void*>& owned) {
   void* d = nullptr;
   size_t n = std::max<size_t>(v.size(), 1) * sizeof(T);
+#ifdef MYO_PLAN_HOST_ONLY   // tools/plan_stats: table sizes without a device (developer tool, never part of the library)
+  d = malloc(n); if (!v.empty()) memcpy(d, v.data(), v.size() * sizeof(T)); owned.push_back(d); return (T*)d;
+#endif
   if (cudaMalloc(&d, n) != cudaSuccess) throw std::string("cudaMalloc failed");
   if (!v.empty() && cudaMemcpy(d, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice) != cudaSuccess)
     throw std::string("cudaMemcpy failed");
