@@ -169,7 +169,7 @@ def main():
 
     def one_step(i):
         if i % FRAME_SKIP == 0:
-            d.ctrl.uniform_(0.0, 1.0, generator=gen)
+            d.storage("ctrl").uniform_(0.0, 1.0, generator=gen)
         mjx.step(model, d, args.nsub)
 
     for i in range(args.warmup):
@@ -185,7 +185,7 @@ def main():
     t_all0.record(stream)
     for i in range(args.steps):
         if i % FRAME_SKIP == 0:
-            d.ctrl.uniform_(0.0, 1.0, generator=gen)
+            d.storage("ctrl").uniform_(0.0, 1.0, generator=gen)
         ev[i][0].record(stream)
         mjx.step(model, d, args.nsub)
         ev[i][1].record(stream)
@@ -205,9 +205,10 @@ def main():
     value = env_steps / (total_ms * 1e-3)
 
     # ---- end to end through the C ABI with host buffers (pinned): H2D state+ctrl, step, D2H state, every step
-    hq = torch.empty((nw, m.nq), dtype=torch.float32).pin_memory(); hv = torch.zeros((nw, m.nv), dtype=torch.float32).pin_memory()
-    ha = torch.zeros((nw, m.na), dtype=torch.float32).pin_memory(); hc = torch.rand((nw, m.nu), dtype=torch.float32).pin_memory()
-    hq.copy_(d.qpos.cpu()); hv.copy_(d.qvel.cpu()); ha.copy_(d.act.cpu())
+    # host buffers in the ABI layout [k][nworld]
+    hq = torch.empty((m.nq, nw), dtype=torch.float32).pin_memory(); hv = torch.zeros((m.nv, nw), dtype=torch.float32).pin_memory()
+    ha = torch.zeros((m.na, nw), dtype=torch.float32).pin_memory(); hc = torch.rand((m.nu, nw), dtype=torch.float32).pin_memory()
+    hq.copy_(d.storage("qpos").cpu()); hv.copy_(d.storage("qvel").cpu()); ha.copy_(d.storage("act").cpu())
     import ctypes
     L = lib.lib()
     vp = ctypes.c_void_p
@@ -262,7 +263,7 @@ def main():
             "data": "synthetic",
             "config": {"workload": WORKLOAD.format(model=args.model, nworld=nw), "nworld_per_gpu": nw, "fields": args.fields,
                        "nsub_per_launch": args.nsub, "frame_skip_ctrl_hold": FRAME_SKIP, "nconmax": d.nconmax, "njmax": d.njmax,
-                       "smem_bytes_per_world": d.smem_bytes, "bytes_per_world_step": bytes_per_world,
+                       "scratch_bytes_per_world": d.smem_bytes, "bytes_per_world_step": bytes_per_world,
                        "l2": "working set per step (%.0f MB) exceeds the 126 MB L2" % (bytes_per_world * nw / 1e6),
                        "partition": "worlds by index, no collective on the step path",
                        "worlds_with_status_flags": int(stats[0].item())},
@@ -270,7 +271,7 @@ def main():
             "e2e": {"value": e2e_value, "unit": "env-steps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "api": "myo_step_host (C ABI, pinned host buffers)", "steps": e2e_steps},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
-                         "peak_source": peak_src, "kernel": "stepKernel<1>", "kernel_ms": kernel_ms,
+                         "peak_source": peak_src, "kernel": "tpwKernel", "kernel_ms": kernel_ms,
                          "algorithmic_bytes_per_launch": bytes_per_world * nw}}
     if not args.no_cpu:
         line["cpu_baseline"] = cpu_baseline(m, os.cpu_count() or 1)

@@ -8,9 +8,11 @@
  * Plain pointers and sizes only; no torch / jax types.  All device work is enqueued on the caller's CUDA
  * stream (passed as void* = cudaStream_t); nothing here synchronises unless stated.
  *
- * Batched layout: every per-world field is a dense row-major array with the WORLD AXIS LEADING
- * ([nworld][k...]), i.e. exactly the layout of a vmapped mjx.Data pytree leaf.  One warp owns one world,
- * so each warp reads and writes contiguous runs.
+ * Batched layout: struct-of-arrays with the WORLD AXIS FASTEST.  A field with k elements per world is one dense
+ * buffer [k][nworld] (element i of world w at base[i * nworld + w]); the logical shape a caller sees is the vmapped
+ * mjx.Data leaf [nworld, k...] as a strided view (torch: buffer.t(); XLA FFI: operand layout minor_to_major with
+ * the world axis minor-most).  One GPU thread owns one world, so the 32 lanes of a warp read and write one
+ * coalesced 128-byte line per element.
  */
 #ifndef MYOSTEP_H_
 #define MYOSTEP_H_
@@ -92,7 +94,7 @@ enum {
 };
 
 /* Batched per-world fields.  State fields are read and written in place by myo_step; the others are
- * outputs (mjData names).  Shapes are per world; dtype float32 unless noted. */
+ * outputs (mjData names).  Shapes are per world ([k] below means a [k][nworld] buffer); dtype float32 unless noted. */
 typedef enum myo_field {
   /* state */
   MYO_F_QPOS = 0,        /* [nq] */
@@ -182,7 +184,7 @@ int myo_batch_create(const myo_model *m, int nworld, int nconmax, int njmax, myo
 void myo_batch_destroy(myo_batch *b);
 int myo_batch_nconmax(const myo_batch *b);
 int myo_batch_njmax(const myo_batch *b);
-int myo_batch_smem_bytes(const myo_batch *b);   /* shared-memory arena per world (one warp) */
+int myo_batch_smem_bytes(const myo_batch *b);   /* bytes of per-world scratch (L1-cached local memory of the world's thread) */
 
 /* Per-world element count / element size of a field for this batch (0 elements = field absent for the model). */
 int64_t myo_field_count(const myo_batch *b, int field);
@@ -191,7 +193,7 @@ int myo_field_is_int(int field);   /* 1: int32 elements, 0: float32 */
 const char *myo_field_name(int field);
 
 /* Bind a caller-owned device buffer (e.g. a DLPack-exported torch / jax array) of
- * nworld * myo_field_count(field) elements to `field`; zero-copy, the library never frees it.
+ * myo_field_count(field) * nworld elements, laid out [count][nworld], to `field`; zero-copy, the library never frees it.
  * dev_ptr == NULL unbinds (an unbound output field is simply not materialised). */
 int myo_batch_bind(myo_batch *b, int field, void *dev_ptr, int64_t nbytes);
 
@@ -209,7 +211,8 @@ int myo_step(myo_batch *b, int nsubsteps, void *cuda_stream);
 int myo_reset(myo_batch *b, const int32_t *world_mask_dev, void *cuda_stream);
 
 /* Host-buffer convenience used by the end-to-end path: H2D of qpos/qvel/act/ctrl (any may be NULL), step,
- * D2H of qpos/qvel/act.  Pinned host memory makes the copies asynchronous; synchronises the stream at the end. */
+ * D2H of qpos/qvel/act, all in the [k][nworld] layout.  Pinned host memory makes the copies asynchronous;
+ * synchronises the stream at the end. */
 int myo_step_host(myo_batch *b, int nsubsteps, const float *qpos, const float *qvel, const float *act,
                   const float *ctrl, float *qpos_out, float *qvel_out, float *act_out, void *cuda_stream);
 

@@ -10,7 +10,6 @@
 #include "devmodel.h"
 #include "internal.h"
 
-int64_t myo_launch_counter();
 
 struct myo_model {
   DevModel D;
@@ -25,7 +24,6 @@ struct myo_batch {
   FieldPtrs F;
   int nworld;
   int slot;      // constant-memory parameter slot
-  int warps;     // worlds per CTA
   bool dirty;    // parameters changed since the last upload
   std::vector<void*> owned;
 };
@@ -102,7 +100,7 @@ int checkReady(myo_batch* b) {
 extern "C" {
 
 const char* myo_last_error(void) { return g_err.c_str(); }
-int64_t myo_launch_count(void) { return myo_launch_counter(); }
+int64_t myo_launch_count(void) { return myo_tpw_launch_counter(); }
 const char* myo_field_name(int field) { return (field >= 0 && field < MYO_F_COUNT) ? kFieldNames[field] : ""; }
 int myo_field_itemsize(int field) { (void)field; return 4; }
 int myo_field_is_int(int field) { return isIntField(field) ? 1 : 0; }
@@ -138,14 +136,13 @@ int myo_batch_create(const myo_model* m, int nworld, int nconmax, int njmax, myo
   if (cudaSetDevice(m->device) != cudaSuccess) return fail(MYO_ERR_CUDA, "cudaSetDevice failed");
   myo_batch* b = new myo_batch();
   b->model = m; b->D = m->D; b->nworld = nworld; b->slot = -1; b->dirty = true;
-  for (int i = 0; i < myo_param_slots(); i++) if (!g_slot_used[i]) { b->slot = i; g_slot_used[i] = true; break; }
+  for (int i = 0; i < myo_tpw_param_slots(); i++) if (!g_slot_used[i]) { b->slot = i; g_slot_used[i] = true; break; }
   if (b->slot < 0) { delete b; return fail(MYO_ERR_ARG, "too many live batches (8 constant-memory parameter slots)"); }
   memset(&b->F, 0, sizeof(b->F));
   try {
     myo_make_layout(b->D, nconmax, njmax, b->L);
   } catch (const std::string& e) { g_slot_used[b->slot] = false; delete b; return fail(MYO_ERR_ARG, e); }
-  b->warps = myo_pick_warps(b->L);
-  if (myo_kernel_smem_bytes(b->L) > 220 * 1024) { g_slot_used[b->slot] = false; delete b; return fail(MYO_ERR_UNSUPPORTED, "model does not fit the per-world shared-memory arena"); }
+  if (b->L.total > myo_tpw_max_scratch()) { g_slot_used[b->slot] = false; delete b; return fail(MYO_ERR_UNSUPPORTED, "model does not fit the largest per-world scratch size class"); }
   // library-owned default state buffers (bind overrides them)
   for (int f : kStateFields) {
     void* p = nullptr;
@@ -165,7 +162,7 @@ void myo_batch_destroy(myo_batch* b) {
 }
 int myo_batch_nconmax(const myo_batch* b) { return b ? b->D.nconmax : 0; }
 int myo_batch_njmax(const myo_batch* b) { return b ? b->D.njmax : 0; }
-int myo_batch_smem_bytes(const myo_batch* b) { return b ? myo_kernel_smem_bytes(b->L) : 0; }
+int myo_batch_smem_bytes(const myo_batch* b) { return b ? b->L.total * 4 : 0; }
 int64_t myo_field_count(const myo_batch* b, int field) { return (b && field >= 0 && field < MYO_F_COUNT) ? fieldCount(b->D, field) : 0; }
 
 int myo_batch_bind(myo_batch* b, int field, void* dev_ptr, int64_t nbytes) {
@@ -187,10 +184,10 @@ static int launch(myo_batch* b, int nsub, int forward_only, const int32_t* mask,
   int rc = checkReady(b);
   if (rc) return rc;
   if (b->dirty) {
-    if (myo_upload_params(b->slot, b->D, b->L, b->F, stream) != 0) return fail(MYO_ERR_CUDA, "parameter upload failed");
+    if (myo_tpw_upload_params(b->slot, b->D, b->L, b->F, stream) != 0) return fail(MYO_ERR_CUDA, "parameter upload failed");
     b->dirty = false;
   }
-  if (myo_launch_step(b->slot, b->L, b->nworld, nsub, forward_only, mask, do_reset, b->warps, stream) != 0)
+  if (myo_tpw_launch_step(b->slot, b->L, b->nworld, nsub, forward_only, mask, do_reset, stream) != 0)
     return fail(MYO_ERR_CUDA, std::string("kernel launch failed: ") + cudaGetErrorString(cudaGetLastError()));
   return MYO_OK;
 }
@@ -227,7 +224,7 @@ int myo_kat_quat(int n, const float* qa, const float* qb, float* prod, float* ma
   if (n <= 0 || !qa || !qb || !prod || !mat || !rotated) return fail(MYO_ERR_ARG, "bad argument");
   int ndev = 0;
   if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return fail(MYO_ERR_CUDA, "no CUDA device: libmyostep has no CPU fallback");
-  return myo_launch_quat_kat(n, qa, qb, prod, mat, rotated, stream) == 0 ? MYO_OK : fail(MYO_ERR_CUDA, "kernel launch failed");
+  return myo_tpw_launch_quat_kat(n, qa, qb, prod, mat, rotated, stream) == 0 ? MYO_OK : fail(MYO_ERR_CUDA, "kernel launch failed");
 }
 
 }  // extern "C"

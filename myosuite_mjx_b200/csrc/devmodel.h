@@ -61,6 +61,7 @@ struct DevModel {
   const float *body_off_pos, *body_off_quat, *body_ipos, *body_iquat, *body_mass, *body_inertia, *body_subtreemass;
   const int *geom_frame, *site_frame;
   const float *geom_lpos, *geom_lquat, *site_lpos, *site_lquat;
+  const float *body_off_mat, *body_imat, *geom_lmat, *site_lmat;   // 3x3 row-major rotations of the offsets above
   // ---- tendons
   const int *unit_tendon, *unit_type, *unit_s0, *unit_s1, *unit_geom, *unit_side, *unit_slot;
   const float *unit_div, *unit_radius;
@@ -76,6 +77,7 @@ struct DevModel {
   const float *act_gear, *act_dynprm, *act_gainprm, *act_biasprm, *act_ctrlrange, *act_forcerange, *act_actrange,
       *act_lengthrange, *act_acc0;
   const float *jnt_stiffness, *qpos_spring;
+  const int *act_same_prm;                     // gainprm == biasprm (one muscle curve evaluation gives gain and bias)
   const int *tact_start, *tact_list;           // [nten+1]: actuators driving each tendon
   const int *dact_start, *dact_list;           // [nv+1]: joint-transmission actuators on each dof
   int any_tendon_passive;
@@ -102,7 +104,7 @@ struct FieldPtrs {
   void *p[MYO_F_COUNT];
 };
 
-// shared-memory layout (float offsets per world), computed on the host
+// per-world scratch layout (float offsets), computed on the host
 struct SmemLayout {
   int total;      // floats per world
   // persistent region
@@ -110,9 +112,9 @@ struct SmemLayout {
       qHinv, tenlen, tenvel, tenJ, actlen, actvel, actforce, actdot, bias, passive, qfrc_act, smooth, qfrc_con, qacc_smooth,
       qacc, warm, tmpv, tforce;
   // overlay region A (tendon stage)
-  int slots, ulen, uwrap;
+  int slots, ulen, uwrap, tmpbody;
   // overlay region B (collision / constraint / solver stage)
-  int cgpose, con, conJ, efc, H, nvec, limrow, basev;
+  int cgpose, con, conJ, efc, H, nvec, limrow, basev, cand;
 };
 
 #endif  // MYO_DEVMODEL_H_

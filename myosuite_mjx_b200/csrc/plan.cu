@@ -282,6 +282,12 @@ void myo_build_plan(const myo_model_desc& m, int nconmax_req, int njmax_req, Dev
     D.body_parent = upload(bpar, owned); D.body_off_pos = upload(bop, owned); D.body_off_quat = upload(boq, owned);
     D.body_ipos = upload(bip, owned); D.body_iquat = upload(biq, owned); D.body_mass = upload(bm, owned);
     D.body_inertia = upload(bin, owned); D.body_subtreemass = upload(bsm, owned);
+    std::vector<float> bom, bim, glm, slm;
+    auto pushm = [](std::vector<float>& v, Q q) { double R[9]; q2m(q, R); for (int k = 0; k < 9; k++) v.push_back((float)R[k]); };
+    for (int b = 0; b < nbody; b++) { pushm(bom, off_quat[b]); pushm(bim, qnorm(ldq(&m.body_iquat[4 * b]))); }
+    for (int g = 0; g < m.ngeom; g++) pushm(glm, qnorm(qmul(off_quat[m.geom_bodyid[g]], ldq(&m.geom_quat[4 * g]))));
+    for (int s = 0; s < m.nsite; s++) pushm(slm, qnorm(qmul(off_quat[m.site_bodyid[s]], ldq(&m.site_quat[4 * s]))));
+    D.body_off_mat = upload(bom, owned); D.body_imat = upload(bim, owned); D.geom_lmat = upload(glm, owned); D.site_lmat = upload(slm, owned);
     std::vector<int> gf(m.ngeom), sf(m.nsite);
     std::vector<float> gp, gq, sp, sq;
     for (int g = 0; g < m.ngeom; g++) {
@@ -394,6 +400,9 @@ void myo_build_plan(const myo_model_desc& m, int nconmax_req, int njmax_req, Dev
         ar[2 * i + k] = (float)m.actuator_actrange[2 * i + k]; lr[2 * i + k] = (float)m.actuator_lengthrange[2 * i + k];
       }
     }
+    std::vector<int> same(nu, 0);
+    for (int i = 0; i < nu; i++) { same[i] = 1; for (int k = 0; k < 9; k++) if (gp[9 * i + k] != bp[9 * i + k]) same[i] = 0; }
+    D.act_same_prm = upload(same, owned);
     D.act_trntype = upload(tt, owned); D.act_trnid = upload(ti, owned); D.act_dyntype = upload(dt, owned); D.act_gaintype = upload(gt, owned);
     D.act_biastype = upload(bt, owned); D.act_flags = upload(fl, owned); D.act_actadr = upload(aa, owned); D.act_gear = upload(gear, owned);
     D.act_dynprm = upload(dp, owned); D.act_gainprm = upload(gp, owned); D.act_biasprm = upload(bp, owned); D.act_ctrlrange = upload(cr, owned);
@@ -596,9 +605,13 @@ void myo_make_layout(DevModel& D, int nconmax_req, int njmax_req, SmemLayout& L)
   L.slots = take(6 * D.nslot); L.ulen = take(D.nunit); L.uwrap = take(D.nunit);
   int endA = o;
   o = base;
+  L.tmpbody = take(13 * D.nbody);   // position-output stage only (before the tendon stage)
+  endA = std::max(endA, o);
+  o = base;
   // overlay B: collision, constraints, solver
   L.cgpose = take(12 * D.ncg); L.con = take(12 * D.nconmax); L.conJ = take(nb * D.nconmax * nv); L.efc = take(10 * D.njmax);
   L.H = take(nv * nv); L.nvec = take(6 * nv); L.limrow = take(2 * (D.nlimj + D.nlimt)); L.basev = take(2 * nb * D.nconmax);
+  L.cand = take(D.npair);
   int endB = o;
   L.total = std::max(endA, endB);
 }

@@ -7,9 +7,11 @@ Mirrors what the reference calls on `mujoco.mjx` (third-party; call sites myosui
     data  = jax.jit(mjx.step)(model, data)     ->  step(model, data)          (vmapped: leading world axis)
     mj_d  = mjx.get_data(mj_model, data)       ->  get_data(model, data)
 
-Field names are mjData's; every `Data` attribute is a torch CUDA tensor `[nworld, ...]` that the kernel reads and
-writes in place (zero-copy: the tensors' storage is bound to the batch through `myo_batch_bind`; any DLPack
-producer can be bound the same way, see `Data.bind`).  `step` returns the same `Data` object; call
+Field names are mjData's; every `Data` attribute is a torch CUDA tensor of logical shape `[nworld, ...]` (the vmapped
+leading axis) that the kernel reads and writes in place.  PHYSICAL layout is struct-of-arrays with the world axis
+fastest (`storage[k, world]`; the attribute is the transposed, strided view), which is what makes every warp access
+one coalesced line.  Zero-copy: the storage is bound to the batch through `myo_batch_bind`; any DLPack producer of a
+`[k, nworld]` buffer can be bound the same way, see `Data.bind`.  `step` returns the same `Data` object; call
 `data.clone()` first if the functional, non-aliasing behaviour of `mjx.step` is needed.
 Unsupported model features raise `NotImplementedError` at `put_model`, as MJX does.  No CPU fallback exists.
 """
@@ -90,14 +92,17 @@ class Data:
             if cnt == 0:
                 continue
             dt = torch.int32 if L.myo_field_is_int(fid) else torch.float32
-            self.bind(name, torch.zeros((self.nworld, cnt), dtype=dt, device=dev))
+            self.bind(name, torch.zeros((cnt, self.nworld), dtype=dt, device=dev))
 
     # -- zero-copy binding of caller-owned device memory (torch tensor or anything exporting __dlpack__)
     def bind(self, name, tensor):
+        """`tensor`: contiguous CUDA storage `[k, nworld]` (world fastest), or its `[nworld, k]` transposed view."""
         if not isinstance(tensor, torch.Tensor):
             tensor = torch.from_dlpack(tensor)
+        if tensor.dim() == 2 and not tensor.is_contiguous() and tensor.t().is_contiguous():
+            tensor = tensor.t()
         if not tensor.is_cuda or not tensor.is_contiguous():
-            raise ValueError("bound buffers must be contiguous CUDA tensors")
+            raise ValueError("bound buffers must be contiguous [k, nworld] CUDA tensors")
         fid = _desc.FIELD_ID[name.lower()]
         _lib.check(_lib.lib().myo_batch_bind(self._h, fid, ctypes.c_void_p(tensor.data_ptr()), tensor.numel() * tensor.element_size()))
         self._t[name.lower()] = tensor
@@ -110,12 +115,19 @@ class Data:
         raise AttributeError(name)
 
     def _view(self, key, t):
+        """storage [k, nworld] -> logical [nworld, ...] strided view (no copy)"""
         shp = _SHAPES.get(key)
         if shp is None:
-            return t
+            return t.t()
         mj = self.model.mj
         dims = [d if isinstance(d, int) else int(getattr(mj, d)) for d in shp]
-        return t.view(self.nworld, *dims)
+        if dims[0] == -1:
+            dims[0] = t.shape[0] // dims[1]
+        return t.view(*dims, self.nworld).permute(len(dims), *range(len(dims)))
+
+    def storage(self, name):
+        """the bound `[k, nworld]` buffer itself"""
+        return self._t[name.lower()]
 
     def fields(self):
         return list(self._t)
@@ -152,7 +164,7 @@ def put_model(mj_model, device=0) -> Model:
 
 def make_data(model, nworld=1, fields="all", nconmax=0, njmax=0) -> Data:
     d = Data(model, nworld, fields, nconmax, njmax)
-    d.qpos[:] = torch.as_tensor(np.asarray(model.mj.qpos0), dtype=torch.float32, device=d.qpos.device)
+    d.storage("qpos").copy_(torch.as_tensor(np.asarray(model.mj.qpos0), dtype=torch.float32, device=d.qpos.device)[:, None].expand(-1, d.nworld))
     return d
 
 
@@ -166,7 +178,7 @@ def put_data(model, mj_data=None, nworld=1, fields="all", nconmax=0, njmax=0) ->
             if v is None:
                 continue
             t = torch.as_tensor(np.asarray(v, dtype=np.float32)).reshape(-1 if np.ndim(v) < 2 else (np.shape(v)[0], -1))
-            getattr(d, name)[:] = t.to(d.qpos.device)
+            getattr(d, name).copy_(t.to(d.qpos.device).expand_as(getattr(d, name)) if t.dim() == 1 else t.to(d.qpos.device))
     return d
 
 
@@ -186,7 +198,7 @@ def step(model, data, nsubsteps=1) -> Data:
 def reset(model, data, mask=None) -> Data:
     """mj_resetData + mj_forward on the masked worlds (reference: myosuite/robot/robot.py:976-979)."""
     if mask is not None:
-        mask = mask.to(device=data.qpos.device, dtype=torch.int32).contiguous()
+        mask = mask.to(device=data.qpos.device, dtype=torch.int32).reshape(-1).contiguous()
     _lib.check(_lib.lib().myo_reset(data._h, ctypes.c_void_p(mask.data_ptr()) if mask is not None else None, _stream()))
     return data
 

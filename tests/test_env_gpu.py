@@ -75,7 +75,7 @@ def test_full_size_properties(models):
     for _ in range(3):
         mjx.step(model, d, 10)
     torch.cuda.synchronize()
-    q = d.qpos.view(rep, 64, -1)
+    q = d.qpos.reshape(rep, 64, -1)
     assert torch.equal(q, q[:1].expand_as(q)), "replicated worlds diverged: the kernel is not world-independent"
     assert torch.isfinite(d.qpos).all() and float(d.qvel.abs().max()) < 1e3
     assert float(d.time.min()) == pytest.approx(30 * 0.002, abs=1e-5)
@@ -93,13 +93,14 @@ def test_step_host_round_trip(models):
     nw = 128
     d = mjx.make_data(model, nw, fields="core")
     e = mjx.make_data(model, nw, fields="core")
-    hq = torch.full((nw, 1), 0.4).pin_memory(); hv = torch.zeros((nw, 1)).pin_memory()
-    ha = torch.zeros((nw, m.na)).pin_memory(); hc = torch.rand((nw, m.nu)).pin_memory()
+    # host buffers in the ABI layout [k][nworld]
+    hq = torch.full((1, nw), 0.4).pin_memory(); hv = torch.zeros((1, nw)).pin_memory()
+    ha = torch.zeros((m.na, nw)).pin_memory(); hc = torch.rand((m.nu, nw)).pin_memory()
     oq = torch.empty_like(hq).pin_memory(); ov = torch.empty_like(hv).pin_memory(); oa = torch.empty_like(ha).pin_memory()
     vp = ctypes.c_void_p
     lib.check(lib.lib().myo_step_host(d._h, 3, vp(hq.data_ptr()), vp(hv.data_ptr()), vp(ha.data_ptr()), vp(hc.data_ptr()),
                                       vp(oq.data_ptr()), vp(ov.data_ptr()), vp(oa.data_ptr()), None))
-    e.qpos.copy_(hq.cuda()); e.ctrl.copy_(hc.cuda())
+    e.storage("qpos").copy_(hq.cuda()); e.storage("ctrl").copy_(hc.cuda())
     mjx.step(model, e, 3)
     torch.cuda.synchronize()
-    assert torch.equal(oq, e.qpos.cpu()) and torch.equal(ov, e.qvel.cpu()) and torch.equal(oa, e.act.cpu())
+    assert torch.equal(oq, e.storage("qpos").cpu()) and torch.equal(ov, e.storage("qvel").cpu()) and torch.equal(oa, e.storage("act").cpu())

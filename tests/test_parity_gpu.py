@@ -197,9 +197,9 @@ def test_bind_errors(models):
     model = mjx.put_model(m)
     d = mjx.make_data(model, 4, fields="core")
     with pytest.raises(lib.MyoError):
-        d.bind("qpos", torch.zeros((4, 7), device="cuda"))          # wrong size
+        d.bind("qpos", torch.zeros((7, 4), device="cuda"))          # wrong size
     with pytest.raises(ValueError):
-        d.bind("qpos", torch.zeros((4, m.nq)))                      # host tensor
+        d.bind("qpos", torch.zeros((m.nq, 4)))                      # host tensor
     assert lib.lib().myo_batch_bind(d._h, 0, None, 0) == -1         # state fields cannot be unbound
     with pytest.raises(lib.MyoError):
         lib.check(lib.lib().myo_step(d._h, 0, None))

@@ -46,5 +46,5 @@ ts = sum(a[0] for a in agg.values()); ti = sum(a[1] for a in agg.values())
 print(f"total samples {ts}  warp-instructions {ti}  sass {sum(a[2] for a in agg.values())}")
 for f, a in sorted(agg.items(), key=lambda kv: -kv[1][0]):
     top = ", ".join(f"{k[6:]} {100*v/max(1,a[0]):.0f}%" for k, v in a[3].most_common(4))
-    nm = re.sub(r"^.*kernels_cu_[0-9a-f]{8}", "", f)[:40]
+    nm = re.sub(r"^.*_cu_[0-9a-f]{8}", "", f)[:40]
     print(f"{100*a[0]/ts:5.1f}%s {100*a[1]/ti:5.1f}%i sass={a[2]:5d}  {nm:50s} {top}")
