@@ -25,6 +25,7 @@ struct myo_batch {
   int nworld;
   int slot;      // constant-memory parameter slot
   bool dirty;    // parameters changed since the last upload
+  float* scratch; // per-world intermediates, [nwarps][L.total][worlds per warp]
   std::vector<void*> owned;
 };
 
@@ -142,7 +143,11 @@ int myo_batch_create(const myo_model* m, int nworld, int nconmax, int njmax, myo
   try {
     myo_make_layout(b->D, nconmax, njmax, b->L);
   } catch (const std::string& e) { g_slot_used[b->slot] = false; delete b; return fail(MYO_ERR_ARG, e); }
-  if (b->L.total > myo_tpw_max_scratch()) { g_slot_used[b->slot] = false; delete b; return fail(MYO_ERR_UNSUPPORTED, "model does not fit the largest per-world scratch size class"); }
+  {
+    void* p = nullptr;
+    if (cudaMalloc(&p, myo_tpw_scratch_floats(b->L, nworld) * sizeof(float)) != cudaSuccess) { g_slot_used[b->slot] = false; delete b; return fail(MYO_ERR_CUDA, "cudaMalloc of the per-world scratch failed"); }
+    b->owned.push_back(p); b->scratch = (float*)p;
+  }
   // library-owned default state buffers (bind overrides them)
   for (int f : kStateFields) {
     void* p = nullptr;
@@ -187,7 +192,7 @@ static int launch(myo_batch* b, int nsub, int forward_only, const int32_t* mask,
     if (myo_tpw_upload_params(b->slot, b->D, b->L, b->F, stream) != 0) return fail(MYO_ERR_CUDA, "parameter upload failed");
     b->dirty = false;
   }
-  if (myo_tpw_launch_step(b->slot, b->L, b->nworld, nsub, forward_only, mask, do_reset, stream) != 0)
+  if (myo_tpw_launch_step(b->slot, b->L, b->nworld, nsub, forward_only, mask, do_reset, b->scratch, stream) != 0)
     return fail(MYO_ERR_CUDA, std::string("kernel launch failed: ") + cudaGetErrorString(cudaGetLastError()));
   return MYO_OK;
 }

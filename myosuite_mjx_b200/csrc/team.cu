@@ -1,0 +1,1835 @@
+// Fused batched mj_step for sm_100a, LANE = WORLD: every thread runs one world's whole step (nsub substeps) as a
+// sequential program; the 32 lanes of a warp execute the same model-table-driven loops on 32 different worlds.
+//
+// Why (measured, profiles/r1a_*): with one warp per world the per-world arena (23 KB for MyoHand) limited an SM to
+// 8 warps, only 10.6 of 32 lanes were active per instruction (tree levels, 23-column factorisations, 39 tendons are
+// narrower than a warp), and scans / shuffles / __syncwarp were a large share of the 125 k warp-instructions per
+// world-step.  With lane = world every model index is warp-uniform (one broadcast load), there is no intra-world
+// synchronisation, lanes diverge only on data (wrap / no wrap, contacts, solver iterations), and all batched fields
+// are struct-of-arrays with the WORLD AXIS FASTEST ([k][nworld]): every load and store of a warp is one coalesced
+// 128-byte line.
+//
+// Per-world intermediates live in a per-thread local array (hardware-interleaved across the lanes of a warp, L1
+// write-back cached, spilling to L2): the same float offsets (SmemLayout) the host plan computes.
+//
+// Replaces (third-party code the reference calls; call sites in include/myostep.h): mj_kinematics, mj_comPos,
+// mj_tendon (+mju_wrap), mj_crb, mj_factorM, mj_collision, mj_makeConstraint, mj_transmission, mj_fwdVelocity,
+// mj_fwdActuation, mj_fwdAcceleration, mj_fwdConstraint (Newton), mj_Euler.
+#include <cuda_runtime.h>
+#include <math_constants.h>
+
+#include <cstdlib>
+
+#include "devmodel.h"
+#include "internal.h"
+
+#define MINVAL 1e-15f
+#ifndef TEAM
+#define TEAM 1   // lanes per world
+#endif
+
+struct TParams { DevModel D; SmemLayout L; FieldPtrs F; };
+#define MYO_NSLOT 8
+__constant__ TParams tP[MYO_NSLOT + 1];   // slot MYO_NSLOT stays zero: "materialise nothing" (inner substeps)
+
+namespace {
+
+enum { JNT_FREE = 0, JNT_BALL = 1, JNT_SLIDE = 2, JNT_HINGE = 3 };
+enum { G_PLANE = 0, G_HFIELD, G_SPHERE, G_CAPSULE, G_ELLIPSOID, G_CYLINDER, G_BOX, G_MESH };
+enum { DYN_NONE = 0, DYN_INTEGRATOR, DYN_FILTER, DYN_FILTEREXACT, DYN_MUSCLE };
+enum { GAIN_FIXED = 0, GAIN_AFFINE, GAIN_MUSCLE };
+enum { BIAS_NONE = 0, BIAS_AFFINE, BIAS_MUSCLE };
+enum { DSBL_CONSTRAINT = 1 << 0, DSBL_EQUALITY = 1 << 1, DSBL_LIMIT = 1 << 3, DSBL_CONTACT = 1 << 4, DSBL_PASSIVE = 1 << 5,
+       DSBL_GRAVITY = 1 << 6, DSBL_CLAMPCTRL = 1 << 7, DSBL_WARMSTART = 1 << 8, DSBL_ACTUATION = 1 << 10 };
+enum { ROW_EQ = 0, ROW_LIMJ = 1, ROW_LIMT = 2, ROW_CON = 3 };
+
+// ------------------------------------------------------------------------------------------ small math
+struct f3 { float x, y, z; };
+__device__ __forceinline__ f3 mk3(float x, float y, float z) { f3 r; r.x = x; r.y = y; r.z = z; return r; }
+__device__ __forceinline__ f3 operator+(f3 a, f3 b) { return mk3(a.x + b.x, a.y + b.y, a.z + b.z); }
+__device__ __forceinline__ f3 operator-(f3 a, f3 b) { return mk3(a.x - b.x, a.y - b.y, a.z - b.z); }
+__device__ __forceinline__ f3 operator*(f3 a, float s) { return mk3(a.x * s, a.y * s, a.z * s); }
+__device__ __forceinline__ float dot(f3 a, f3 b) { return fmaf(a.x, b.x, fmaf(a.y, b.y, a.z * b.z)); }
+__device__ __forceinline__ f3 cross(f3 a, f3 b) { return mk3(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x); }
+__device__ __forceinline__ float norm3(f3 a) { return sqrtf(dot(a, a)); }
+template <class P> __device__ __forceinline__ f3 ld3(P p) { return mk3(p[0], p[1], p[2]); }
+template <class P> __device__ __forceinline__ void st3(P p, f3 v) { p[0] = v.x; p[1] = v.y; p[2] = v.z; }
+__device__ __forceinline__ f3 unit3(f3 a) {
+  float n = norm3(a);
+  return n < MINVAL ? mk3(1.f, 0.f, 0.f) : a * (1.f / n);
+}
+template <class P> __device__ __forceinline__ f3 mulM(P R, f3 v) {
+  return mk3(fmaf(R[0], v.x, fmaf(R[1], v.y, R[2] * v.z)), fmaf(R[3], v.x, fmaf(R[4], v.y, R[5] * v.z)),
+             fmaf(R[6], v.x, fmaf(R[7], v.y, R[8] * v.z)));
+}
+template <class P> __device__ __forceinline__ f3 mulMT(P R, f3 v) {
+  return mk3(fmaf(R[0], v.x, fmaf(R[3], v.y, R[6] * v.z)), fmaf(R[1], v.x, fmaf(R[4], v.y, R[7] * v.z)),
+             fmaf(R[2], v.x, fmaf(R[5], v.y, R[8] * v.z)));
+}
+struct f4 { float w, x, y, z; };
+template <class P> __device__ __forceinline__ f4 ld4(P p) { f4 q; q.w = p[0]; q.x = p[1]; q.y = p[2]; q.z = p[3]; return q; }
+template <class P> __device__ __forceinline__ void st4(P p, f4 q) { p[0] = q.w; p[1] = q.x; p[2] = q.y; p[3] = q.z; }
+__device__ __forceinline__ f4 qmul(f4 a, f4 b) {
+  f4 r;
+  r.w = a.w * b.w - a.x * b.x - a.y * b.y - a.z * b.z;
+  r.x = a.w * b.x + a.x * b.w + a.y * b.z - a.z * b.y;
+  r.y = a.w * b.y - a.x * b.z + a.y * b.w + a.z * b.x;
+  r.z = a.w * b.z + a.x * b.y - a.y * b.x + a.z * b.w;
+  return r;
+}
+__device__ __forceinline__ f4 qnormalize(f4 q) {
+  float n = sqrtf(q.w * q.w + q.x * q.x + q.y * q.y + q.z * q.z);
+  if (n < MINVAL) { q.w = 1.f; q.x = q.y = q.z = 0.f; return q; }
+  float s = 1.f / n;
+  q.w *= s; q.x *= s; q.y *= s; q.z *= s;
+  return q;
+}
+__device__ __forceinline__ void q2m(float* R, f4 q) {
+  float w = q.w, x = q.x, y = q.y, z = q.z;
+  R[0] = w * w + x * x - y * y - z * z; R[1] = 2.f * (x * y - w * z); R[2] = 2.f * (x * z + w * y);
+  R[3] = 2.f * (x * y + w * z); R[4] = w * w - x * x + y * y - z * z; R[5] = 2.f * (y * z - w * x);
+  R[6] = 2.f * (x * z - w * y); R[7] = 2.f * (y * z + w * x); R[8] = w * w - x * x - y * y + z * z;
+}
+// C = A * B (row-major 3x3)
+template <class PC, class PA, class PB> __device__ __forceinline__ void mulMM(PC C, PA A, PB B) {
+#pragma unroll
+  for (int i = 0; i < 3; i++)
+#pragma unroll
+    for (int j = 0; j < 3; j++) C[3 * i + j] = fmaf(A[3 * i], B[j], fmaf(A[3 * i + 1], B[3 + j], A[3 * i + 2] * B[6 + j]));
+}
+__device__ __forceinline__ float clipf(float x, float lo, float hi) { return fminf(fmaxf(x, lo), hi); }
+// spatial algebra on [angular; linear] 6-vectors; inertia = (Ixx Iyy Izz Ixy Ixz Iyz, m*cx m*cy m*cz, m)
+template <class PR, class PI, class PV> __device__ __forceinline__ void inertMulVec(PR r, PI I, PV v) {
+  f3 w = ld3(v), l = ld3(v + 3), mc = ld3(I + 6);
+  f3 Iw = mk3(I[0] * w.x + I[3] * w.y + I[4] * w.z, I[3] * w.x + I[1] * w.y + I[5] * w.z, I[4] * w.x + I[5] * w.y + I[2] * w.z);
+  st3(r, Iw + cross(mc, l));
+  st3(r + 3, l * I[9] + cross(w, mc));
+}
+template <class PR, class PA, class PB> __device__ __forceinline__ void crossMotion(PR r, PA vel, PB v) {
+  f3 w = ld3(vel), l = ld3(vel + 3), a = ld3(v), b = ld3(v + 3);
+  st3(r, cross(w, a)); st3(r + 3, cross(w, b) + cross(l, a));
+}
+template <class PR, class PA, class PB> __device__ __forceinline__ void crossForce(PR r, PA vel, PB f) {
+  f3 w = ld3(vel), l = ld3(vel + 3), a = ld3(f), b = ld3(f + 3);
+  st3(r, cross(w, a) + cross(l, b)); st3(r + 3, cross(w, b));
+}
+
+// one out-of-line copy of each heavy libm routine
+__device__ __noinline__ void sincos_(float x, float* s, float* c) { sincosf(x, s, c); }
+__device__ __noinline__ float asin_(float x) { return asinf(x); }
+__device__ __noinline__ float acos_(float x) { return acosf(x); }
+__device__ __noinline__ float pow_(float x, float y) { return powf(x, y); }
+__device__ __noinline__ float cos_(float x) { return cosf(x); }
+__device__ __noinline__ float sin_(float x) { return sinf(x); }
+
+// Per-world scratch: every world owns SmemLayout.total floats, stored interleaved over the SCR_STRIDE worlds that
+// share a warp (element k of the warp's world g at warp_base[k * SCR_STRIDE + g]), so one scratch access of a warp
+// is one coalesced line.  SP is a strided pointer into it.
+#define SCR_STRIDE (32 / TEAM)
+struct SP {
+  float* p;
+  __device__ __forceinline__ float& operator[](int i) const { return p[i * SCR_STRIDE]; }
+  __device__ __forceinline__ SP operator+(int k) const { SP r; r.p = p + k * SCR_STRIDE; return r; }
+};
+struct SPI {
+  int* p;
+  __device__ __forceinline__ int& operator[](int i) const { return p[i * SCR_STRIDE]; }
+};
+__device__ __forceinline__ SPI asInt(SP s) { SPI r; r.p = (int*)s.p; return r; }
+
+// frame record in the per-world scratch: pos[3], quat[4], mat[9]
+#define FR_POS(sm, L, f) ((sm) + (L).frames + 16 * (f))
+#define FR_QUAT(sm, L, f) ((sm) + (L).frames + 16 * (f) + 3)
+#define FR_MAT(sm, L, f) ((sm) + (L).frames + 16 * (f) + 7)
+
+// batched field access, struct-of-arrays, world fastest: element k of world w lives at base[k * nworld + w]
+struct World { size_t w, nw; };
+#define OUTF(ptr, k) ((float*)(ptr))[(size_t)(k) * W.nw + W.w]
+#define OUTI(ptr, k) ((int*)(ptr))[(size_t)(k) * W.nw + W.w]
+
+// ------------------------------------------------------------------------------------------ kinematics
+__device__ __noinline__ void kinematics(int slot, SP sm) {
+  const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
+  {
+    auto p = FR_POS(sm, L, 0);
+    p[0] = p[1] = p[2] = 0.f; p[3] = 1.f; p[4] = p[5] = p[6] = 0.f;
+    p[7] = 1.f; p[8] = 0.f; p[9] = 0.f; p[10] = 0.f; p[11] = 1.f; p[12] = 0.f; p[13] = 0.f; p[14] = 0.f; p[15] = 1.f;
+  }
+  auto qpos = sm + L.qpos;
+  // #pragma unroll 1
+  for (int f = 1; f < D.nframe; f++) {   // frames are in depth-first order: parents come first
+    const int p = D.fr_parent[f], ja = D.fr_jntadr[f], jn = D.fr_jntnum[f];
+    f3 pos; f4 quat; float R[9];
+    if (jn == 1 && D.jnt_type[ja] == JNT_FREE) {
+      const int qa = D.jnt_qposadr[ja];
+      pos = ld3(qpos + qa);
+      quat = qnormalize(ld4(qpos + qa + 3));
+      st4(qpos + qa + 3, quat);
+      st3(sm + L.xanchor + 3 * ja, pos); st3(sm + L.xaxis + 3 * ja, ld3(D.jnt_axis + 3 * ja));
+    } else {
+      pos = ld3(FR_POS(sm, L, p)) + mulM(FR_MAT(sm, L, p), ld3(D.fr_pre_pos + 3 * f));
+      quat = qmul(ld4(FR_QUAT(sm, L, p)), ld4(D.fr_pre_quat + 4 * f));
+      q2m(R, quat);
+      // #pragma unroll 1
+      for (int j = ja; j < ja + jn; j++) {
+        const f3 lpos = ld3(D.jnt_pos + 3 * j), laxis = ld3(D.jnt_axis + 3 * j);
+        const f3 anchor = mulM(R, lpos) + pos, axis = mulM(R, laxis);
+        st3(sm + L.xanchor + 3 * j, anchor); st3(sm + L.xaxis + 3 * j, axis);
+        const int qa = D.jnt_qposadr[j];
+        const float d = qpos[qa] - D.qpos0[qa];
+        if (D.jnt_type[j] == JNT_SLIDE) pos = pos + axis * d;
+        else {
+          float sn, cs; sincos_(0.5f * d, &sn, &cs);
+          f4 ql; ql.w = cs; ql.x = laxis.x * sn; ql.y = laxis.y * sn; ql.z = laxis.z * sn;
+          quat = qmul(quat, ql);
+          q2m(R, quat);
+          pos = anchor - mulM(R, lpos);
+        }
+      }
+    }
+    quat = qnormalize(quat);
+    q2m(R, quat);
+    auto o = FR_POS(sm, L, f);
+    st3(o, pos); st4(o + 3, quat);
+#pragma unroll
+    for (int k = 0; k < 9; k++) o[7 + k] = R[k];
+  }
+}
+
+// composite inertia of every frame about its tree's centre of mass, motion axes (mj_comPos over weld groups)
+__device__ __noinline__ void comPos(int slot, SP sm) {
+  const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
+  auto cin = sm + L.cinert;
+  // #pragma unroll 1
+  for (int f = 0; f < D.nframe; f++) {
+    f3 cw = ld3(FR_POS(sm, L, f)) + mulM(FR_MAT(sm, L, f), ld3(D.fr_com + 3 * f));
+    st3(cin + 10 * f + 6, cw); cin[10 * f + 9] = D.fr_mass[f];
+  }
+  // #pragma unroll 1
+  for (int r = 0; r < D.nroot; r++) {
+    f3 acc = ld3(D.root_const + 4 * r);
+    const float M = D.root_const[4 * r + 3];
+    // #pragma unroll 1
+    for (int f = D.root_fstart[r]; f < D.root_fend[r]; f++) acc = acc + ld3(cin + 10 * f + 6) * cin[10 * f + 9];
+    if (M < MINVAL) acc = mk3(0.f, 0.f, 0.f); else acc = acc * (1.f / M);
+    st3(sm + L.rootcom + 3 * r, acc);
+  }
+  // #pragma unroll 1
+  for (int f = 0; f < D.nframe; f++) {
+    auto c = cin + 10 * f;
+    if (f == 0) { for (int k = 0; k < 10; k++) c[k] = 0.f; continue; }
+    auto R = FR_MAT(sm, L, f);
+    auto I = D.fr_inertia + 6 * f;
+    const float m = c[9];
+    const f3 off = ld3(c + 6) - ld3(sm + L.rootcom + 3 * D.fr_root[f]);
+    float T[9];
+#pragma unroll
+    for (int i = 0; i < 3; i++) {
+      T[3 * i] = R[3 * i] * I[0] + R[3 * i + 1] * I[3] + R[3 * i + 2] * I[4];
+      T[3 * i + 1] = R[3 * i] * I[3] + R[3 * i + 1] * I[1] + R[3 * i + 2] * I[5];
+      T[3 * i + 2] = R[3 * i] * I[4] + R[3 * i + 1] * I[5] + R[3 * i + 2] * I[2];
+    }
+    const float xx = T[0] * R[0] + T[1] * R[1] + T[2] * R[2], yy = T[3] * R[3] + T[4] * R[4] + T[5] * R[5],
+                zz = T[6] * R[6] + T[7] * R[7] + T[8] * R[8], xy = T[0] * R[3] + T[1] * R[4] + T[2] * R[5],
+                xz = T[0] * R[6] + T[1] * R[7] + T[2] * R[8], yz = T[3] * R[6] + T[4] * R[7] + T[5] * R[8];
+    c[0] = xx + m * (off.y * off.y + off.z * off.z); c[1] = yy + m * (off.x * off.x + off.z * off.z);
+    c[2] = zz + m * (off.x * off.x + off.y * off.y); c[3] = xy - m * off.x * off.y; c[4] = xz - m * off.x * off.z;
+    c[5] = yz - m * off.y * off.z; c[6] = m * off.x; c[7] = m * off.y; c[8] = m * off.z;
+  }
+  // #pragma unroll 1
+  for (int j = 0; j < D.njnt; j++) {
+    const int f = D.jnt_frame[j], da = D.jnt_dofadr[j];
+    const f3 off = ld3(sm + L.rootcom + 3 * D.fr_root[f]) - ld3(sm + L.xanchor + 3 * j);
+    const f3 axis = ld3(sm + L.xaxis + 3 * j);
+    auto cd = sm + L.cdof + 6 * da;
+    const int ty = D.jnt_type[j];
+    if (ty == JNT_FREE) {
+      auto R = FR_MAT(sm, L, f);
+#pragma unroll
+      for (int k = 0; k < 3; k++) {
+        st3(cd + 6 * k, mk3(0.f, 0.f, 0.f)); st3(cd + 6 * k + 3, mk3(k == 0, k == 1, k == 2));
+        const f3 ax = mk3(R[k], R[3 + k], R[6 + k]);
+        st3(cd + 6 * (3 + k), ax); st3(cd + 6 * (3 + k) + 3, cross(ax, off));
+      }
+    } else if (ty == JNT_SLIDE) {
+      st3(cd, mk3(0.f, 0.f, 0.f)); st3(cd + 3, axis);
+    } else {
+      st3(cd, axis); st3(cd + 3, cross(axis, off));
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------ mjData position outputs
+// Written straight to global memory (struct-of-arrays, coalesced across the warp's worlds); nothing here feeds the dynamics.
+__device__ __noinline__ void writePositionOutputs(int slot, int fslot, SP sm, World W) {
+  const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L; const FieldPtrs& F = tP[fslot].F;
+  void* xpos = F.p[MYO_F_XPOS]; void* xquat = F.p[MYO_F_XQUAT]; void* xmat = F.p[MYO_F_XMAT];
+  void* xipos = F.p[MYO_F_XIPOS]; void* ximat = F.p[MYO_F_XIMAT]; void* cinert = F.p[MYO_F_CINERT];
+  void* scom = F.p[MYO_F_SUBTREE_COM]; void* crb = F.p[MYO_F_CRB];
+  const int nb = D.nbody;
+  auto tb = sm + L.tmpbody;   // [nbody][13]: mass-weighted com accumulators (3) + body-level cinert (10)
+  if (xpos || xquat || xmat || xipos || ximat || cinert || scom || crb) {
+    // #pragma unroll 1
+    for (int b = 0; b < nb; b++) {
+      const int f = D.body_frame[b];
+      auto R = FR_MAT(sm, L, f);
+      const f3 pos = ld3(FR_POS(sm, L, f)) + mulM(R, ld3(D.body_off_pos + 3 * b));
+      float M[9]; mulMM(M, R, D.body_off_mat + 9 * b);
+      if (xpos) { OUTF(xpos, 3 * b) = pos.x; OUTF(xpos, 3 * b + 1) = pos.y; OUTF(xpos, 3 * b + 2) = pos.z; }
+      if (xquat) {
+        const f4 q = qnormalize(qmul(ld4(FR_QUAT(sm, L, f)), ld4(D.body_off_quat + 4 * b)));
+        OUTF(xquat, 4 * b) = q.w; OUTF(xquat, 4 * b + 1) = q.x; OUTF(xquat, 4 * b + 2) = q.y; OUTF(xquat, 4 * b + 3) = q.z;
+      }
+      if (xmat)
+#pragma unroll
+        for (int k = 0; k < 9; k++) OUTF(xmat, 9 * b + k) = M[k];
+      const f3 ip = pos + mulM(M, ld3(D.body_ipos + 3 * b));
+      if (xipos) { OUTF(xipos, 3 * b) = ip.x; OUTF(xipos, 3 * b + 1) = ip.y; OUTF(xipos, 3 * b + 2) = ip.z; }
+      const float m = D.body_mass[b];
+      auto t = tb + 13 * b;
+      const bool massless = D.body_subtreemass[b] < MINVAL;   // MuJoCo: subtree_com of a massless subtree = xipos
+      t[0] = massless ? ip.x : m * ip.x; t[1] = massless ? ip.y : m * ip.y; t[2] = massless ? ip.z : m * ip.z;
+      if (ximat || cinert || crb) {
+        float IM[9]; mulMM(IM, M, D.body_imat + 9 * b);
+        if (ximat)
+#pragma unroll
+          for (int k = 0; k < 9; k++) OUTF(ximat, 9 * b + k) = IM[k];
+        auto c = t + 3;
+        if (b == 0) { for (int k = 0; k < 10; k++) c[k] = 0.f; }
+        else {
+          const float i0 = D.body_inertia[3 * b], i1 = D.body_inertia[3 * b + 1], i2 = D.body_inertia[3 * b + 2];
+          const f3 off = ip - ld3(sm + L.rootcom + 3 * D.body_root[b]);
+          c[0] = IM[0] * IM[0] * i0 + IM[1] * IM[1] * i1 + IM[2] * IM[2] * i2 + m * (off.y * off.y + off.z * off.z);
+          c[1] = IM[3] * IM[3] * i0 + IM[4] * IM[4] * i1 + IM[5] * IM[5] * i2 + m * (off.x * off.x + off.z * off.z);
+          c[2] = IM[6] * IM[6] * i0 + IM[7] * IM[7] * i1 + IM[8] * IM[8] * i2 + m * (off.x * off.x + off.y * off.y);
+          c[3] = IM[0] * IM[3] * i0 + IM[1] * IM[4] * i1 + IM[2] * IM[5] * i2 - m * off.x * off.y;
+          c[4] = IM[0] * IM[6] * i0 + IM[1] * IM[7] * i1 + IM[2] * IM[8] * i2 - m * off.x * off.z;
+          c[5] = IM[3] * IM[6] * i0 + IM[4] * IM[7] * i1 + IM[5] * IM[8] * i2 - m * off.y * off.z;
+          c[6] = m * off.x; c[7] = m * off.y; c[8] = m * off.z; c[9] = m;
+        }
+        if (cinert)
+#pragma unroll
+          for (int k = 0; k < 10; k++) OUTF(cinert, 10 * b + k) = c[k];
+      }
+    }
+    if (scom || crb) {
+      // subtree sums by one backward sweep (bodies are depth-first: parent index < child index)
+      // #pragma unroll 1
+      for (int b = nb - 1; b >= 0; b--) {
+        auto t = tb + 13 * b;
+        if (scom) {
+          const float Ms = D.body_subtreemass[b];
+          const f3 c = Ms < MINVAL ? mk3(t[0], t[1], t[2]) : mk3(t[0], t[1], t[2]) * (1.f / Ms);
+          OUTF(scom, 3 * b) = c.x; OUTF(scom, 3 * b + 1) = c.y; OUTF(scom, 3 * b + 2) = c.z;
+        }
+        if (crb)
+#pragma unroll
+          for (int k = 0; k < 10; k++) OUTF(crb, 10 * b + k) = b > 0 ? t[3 + k] : 0.f;
+        if (b > 0) {
+          auto tp = tb + 13 * D.body_parent[b];
+          if (!(D.body_subtreemass[b] < MINVAL)) for (int k = 0; k < 3; k++) tp[k] += t[k];
+          if (crb && D.body_parent[b] > 0) for (int k = 3; k < 13; k++) tp[k] += t[k];
+        }
+      }
+    }
+  }
+  void* xa = F.p[MYO_F_XANCHOR]; void* xx = F.p[MYO_F_XAXIS];
+  if (xa) for (int i = 0; i < 3 * D.njnt; i++) OUTF(xa, i) = sm[L.xanchor + i];
+  if (xx) for (int i = 0; i < 3 * D.njnt; i++) OUTF(xx, i) = sm[L.xaxis + i];
+  void* cd = F.p[MYO_F_CDOF];
+  if (cd) for (int i = 0; i < 6 * D.nv; i++) OUTF(cd, i) = sm[L.cdof + i];
+  void* gp = F.p[MYO_F_GEOM_XPOS]; void* gm = F.p[MYO_F_GEOM_XMAT];
+  if (gp || gm) {
+    // #pragma unroll 1
+    for (int g = 0; g < D.ngeom; g++) {
+      const int f = D.geom_frame[g];
+      auto R = FR_MAT(sm, L, f);
+      if (gp) {
+        const f3 p = ld3(FR_POS(sm, L, f)) + mulM(R, ld3(D.geom_lpos + 3 * g));
+        OUTF(gp, 3 * g) = p.x; OUTF(gp, 3 * g + 1) = p.y; OUTF(gp, 3 * g + 2) = p.z;
+      }
+      if (gm) {
+        float M[9]; mulMM(M, R, D.geom_lmat + 9 * g);
+#pragma unroll
+        for (int k = 0; k < 9; k++) OUTF(gm, 9 * g + k) = M[k];
+      }
+    }
+  }
+  void* sp = F.p[MYO_F_SITE_XPOS]; void* smt = F.p[MYO_F_SITE_XMAT];
+  if (sp || smt) {
+    // #pragma unroll 1
+    for (int s = 0; s < D.nsite; s++) {
+      const int f = D.site_frame[s];
+      auto R = FR_MAT(sm, L, f);
+      if (sp) {
+        const f3 p = ld3(FR_POS(sm, L, f)) + mulM(R, ld3(D.site_lpos + 3 * s));
+        OUTF(sp, 3 * s) = p.x; OUTF(sp, 3 * s + 1) = p.y; OUTF(sp, 3 * s + 2) = p.z;
+      }
+      if (smt) {
+        float M[9]; mulMM(M, R, D.site_lmat + 9 * s);
+#pragma unroll
+        for (int k = 0; k < 9; k++) OUTF(smt, 9 * s + k) = M[k];
+      }
+    }
+  }
+}
+// ------------------------------------------------------------------------------------------ tendon wrapping (mju_wrap)
+__device__ __forceinline__ bool segIntersect(const float* p1, const float* p2, const float* p3, const float* p4) {
+  const float det = (p4[1] - p3[1]) * (p2[0] - p1[0]) - (p4[0] - p3[0]) * (p2[1] - p1[1]);
+  if (fabsf(det) < MINVAL) return false;
+  const float a = ((p4[0] - p3[0]) * (p1[1] - p3[1]) - (p4[1] - p3[1]) * (p1[0] - p3[0])) / det;
+  const float b = ((p2[0] - p1[0]) * (p1[1] - p3[1]) - (p2[1] - p1[1]) * (p1[0] - p3[0])) / det;
+  return a >= 0.f && a <= 1.f && b >= 0.f && b <= 1.f;
+}
+__device__ __noinline__ float wrapCircle(float* pnt, const float* d, const float* sd, float rad) {
+  const float sq0 = d[0] * d[0] + d[1] * d[1], sq1 = d[2] * d[2] + d[3] * d[3], sqr = rad * rad;
+  const float dx = d[2] - d[0], dy = d[3] - d[1];
+  const float dd = dx * dx + dy * dy;
+  float a = -(dx * d[0] + dy * d[1]) / fmaxf(MINVAL, dd);
+  a = clipf(a, 0.f, 1.f);
+  const float nx = d[0] + a * dx, ny = d[1] + a * dy;
+  if (nx * nx + ny * ny > sqr && (!sd || sd[0] * nx + sd[1] * ny >= 0.f)) return -1.f;
+  if (sq0 < sqr || sq1 < sqr) return -1.f;
+  const float s0 = sqrtf(sq0 - sqr), s1 = sqrtf(sq1 - sqr);
+  float sol[2][4], good[2];
+#pragma unroll
+  for (int i = 0; i < 2; i++) {
+    const float sg = i == 0 ? 1.f : -1.f;
+    sol[i][0] = (d[0] * sqr + sg * rad * d[1] * s0) / sq0;
+    sol[i][1] = (d[1] * sqr - sg * rad * d[0] * s0) / sq0;
+    sol[i][2] = (d[2] * sqr - sg * rad * d[3] * s1) / sq1;
+    sol[i][3] = (d[3] * sqr + sg * rad * d[2] * s1) / sq1;
+    if (sd) {
+      const float tx = sol[i][0] + sol[i][2], ty = sol[i][1] + sol[i][3];
+      good[i] = (tx * sd[0] + ty * sd[1]) / fmaxf(MINVAL, sqrtf(tx * tx + ty * ty));
+    } else {
+      const float tx = sol[i][0] - sol[i][2], ty = sol[i][1] - sol[i][3];
+      good[i] = -(tx * tx + ty * ty);
+    }
+    if (segIntersect(d, sol[i], d + 2, sol[i] + 2)) good[i] = -10000.f;
+  }
+  const int i = good[0] > good[1] ? 0 : 1;
+#pragma unroll
+  for (int k = 0; k < 4; k++) pnt[k] = i == 0 ? sol[0][k] : sol[1][k];
+  if (segIntersect(d, pnt, d + 2, pnt + 2)) return -1.f;
+  const float n0 = fmaxf(MINVAL, sqrtf(pnt[0] * pnt[0] + pnt[1] * pnt[1])), n1 = fmaxf(MINVAL, sqrtf(pnt[2] * pnt[2] + pnt[3] * pnt[3]));
+  float ang = acos_(clipf((pnt[0] * pnt[2] + pnt[1] * pnt[3]) / (n0 * n1), -1.f, 1.f));
+  const float cr = pnt[1] * pnt[2] - pnt[0] * pnt[3];
+  if ((cr > 0.f && i) || (cr < 0.f && !i)) ang = 2.f * CUDART_PI_F - ang;
+  return rad * ang;
+}
+__device__ __noinline__ float wrapInside(float* pnt, const float* d, float rad) {
+  const float l0 = sqrtf(d[0] * d[0] + d[1] * d[1]), l1 = sqrtf(d[2] * d[2] + d[3] * d[3]);
+  if (l0 <= rad || l1 <= rad) return -1.f;
+  const float dx = d[2] - d[0], dy = d[3] - d[1];
+  const float dd = dx * dx + dy * dy;
+  if (dd > MINVAL) {
+    const float a = -(dx * d[0] + dy * d[1]) / dd;
+    if (a > 0.f && a < 1.f) {
+      const float tx = d[0] + a * dx, ty = d[1] + a * dy;
+      if (sqrtf(tx * tx + ty * ty) <= rad) return -1.f;
+    }
+  }
+  const float mx = 0.5f * (d[0] + d[2]), my = 0.5f * (d[1] + d[3]);
+  const float mn = fmaxf(MINVAL, sqrtf(mx * mx + my * my));
+  pnt[0] = pnt[2] = rad * mx / mn; pnt[1] = pnt[3] = rad * my / mn;
+  const float A = rad / l0, B = rad / l1;
+  const float cosG = (l0 * l0 + l1 * l1 - dd) / (2.f * l0 * l1);
+  if (cosG < -1.f + 1e-7f) return -1.f;
+  if (cosG > 1.f - 1e-7f) return 0.f;
+  const float G = acos_(cosG);
+  // Root of asin(A z) + asin(B z) - 2 asin(z) + G on z in (0,1).  MuJoCo iterates on z from z = 1 - 1e-7, where
+  // d/dz blows up and float32 cannot resolve the root; we iterate on t = acos(z) instead (same function, same
+  // root, same bail-out tests translated: df/dz > 0 <=> dg/dt < 0, z increasing <=> t decreasing).
+  float t = 4.4721e-4f;  // acos(1 - 1e-7)
+  float ct = cos_(t);
+  float f = asin_(A * ct) + asin_(B * ct) + 2.f * t - CUDART_PI_F + G;
+  if (f > 0.f) return 0.f;
+  int it = 0;
+  // #pragma unroll 1
+  for (; it < 20 && fabsf(f) > 1e-6f; it++) {
+    const float st = sin_(t);
+    const float dg = 2.f - st * (A / fmaxf(1e-12f, sqrtf(1.f - ct * ct * A * A)) + B / fmaxf(1e-12f, sqrtf(1.f - ct * ct * B * B)));
+    if (dg < 1e-12f) return 0.f;
+    const float t1 = t - f / dg;
+    if (t1 < t) return 0.f;
+    t = t1; ct = cos_(t);
+    f = asin_(A * ct) + asin_(B * ct) + 2.f * t - CUDART_PI_F + G;
+    if (f > 1e-5f) return 0.f;
+  }
+  if (it >= 20) return 0.f;
+  float vx, vy, ang;
+  if (d[0] * d[3] - d[1] * d[2] > 0.f) { vx = d[0] / l0; vy = d[1] / l0; ang = 0.5f * CUDART_PI_F - t - asin_(A * ct); }
+  else { vx = d[2] / l1; vy = d[3] / l1; ang = 0.5f * CUDART_PI_F - t - asin_(B * ct); }
+  float sn, cs; sincos_(ang, &sn, &cs);
+  pnt[0] = pnt[2] = rad * (cs * vx - sn * vy);
+  pnt[1] = pnt[3] = rad * (sn * vx + cs * vy);
+  return 0.f;
+}
+// returns wrap length or -1; w0/w1 = world tangent points
+__device__ __noinline__ float wrapGeom(f3 x0, f3 x1, f3 gpos, const float* gmat, float radius, int type, bool hasSide, f3 side, f3* w0, f3* w1) {
+  if (radius < MINVAL) return -1.f;
+  const f3 p0 = mulMT(gmat, x0 - gpos), p1 = mulMT(gmat, x1 - gpos);
+  if (norm3(p0) < MINVAL || norm3(p1) < MINVAL) return -1.f;
+  f3 ax0, ax1;
+  if (type == UNIT_SPHERE) {
+    ax0 = unit3(p0);
+    f3 nrm = cross(p0, p1);
+    const float n = norm3(nrm);
+    if (n < MINVAL) {
+      const float a0 = fabsf(ax0.x), a1 = fabsf(ax0.y), a2 = fabsf(ax0.z);
+      const int k = (a0 >= a1 && a0 >= a2) ? 0 : (a1 >= a2 ? 1 : 2);
+      nrm = unit3(cross(ax0, mk3(k != 0, k != 1, k != 2)));
+    } else nrm = nrm * (1.f / n);
+    ax1 = unit3(cross(nrm, ax0));
+  } else { ax0 = mk3(1.f, 0.f, 0.f); ax1 = mk3(0.f, 1.f, 0.f); }
+  float d[4] = {dot(p0, ax0), dot(p0, ax1), dot(p1, ax0), dot(p1, ax1)};
+  float sd[2] = {0.f, 0.f};
+  bool inside = false;
+  if (hasSide) {
+    const f3 s = mulMT(gmat, side - gpos);
+    sd[0] = dot(s, ax0); sd[1] = dot(s, ax1);
+    const float n = radius / fmaxf(MINVAL, sqrtf(sd[0] * sd[0] + sd[1] * sd[1]));
+    sd[0] *= n; sd[1] *= n;
+    inside = norm3(s) < radius;
+  }
+  float pnt[4];
+  float wlen = inside ? wrapInside(pnt, d, radius) : wrapCircle(pnt, d, hasSide ? sd : nullptr, radius);
+  if (wlen < 0.f) return -1.f;
+  f3 r0 = ax0 * pnt[0] + ax1 * pnt[1], r1 = ax0 * pnt[2] + ax1 * pnt[3];
+  if (type == UNIT_CYLINDER) {
+    const float L0 = sqrtf((p0.x - r0.x) * (p0.x - r0.x) + (p0.y - r0.y) * (p0.y - r0.y));
+    const float L1 = sqrtf((p1.x - r1.x) * (p1.x - r1.x) + (p1.y - r1.y) * (p1.y - r1.y));
+    const float tot = fmaxf(MINVAL, L0 + wlen + L1);
+    r0.z = p0.z + (p1.z - p0.z) * L0 / tot;
+    r1.z = p0.z + (p1.z - p0.z) * (L0 + wlen) / tot;
+    const float h = r1.z - r0.z;
+    wlen = sqrtf(wlen * wlen + h * h);
+  }
+  *w0 = mulM(gmat, r0) + gpos; *w1 = mulM(gmat, r1) + gpos;
+  return wlen;
+}
+
+// mj_tendon: path lengths + sparse moment arms
+__device__ __noinline__ void tendons(int slot, int fslot, SP sm, World W) {
+  const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L; const FieldPtrs& F = tP[fslot].F;
+  // #pragma unroll 1
+  for (int u = 0; u < D.nunit; u++) {
+    const int s0 = D.unit_s0[u], s1 = D.unit_s1[u], g = D.unit_geom[u];
+    const int f0 = D.site_frame[s0], f1 = D.site_frame[s1];
+    const f3 p0 = ld3(FR_POS(sm, L, f0)) + mulM(FR_MAT(sm, L, f0), ld3(D.site_lpos + 3 * s0));
+    const f3 p1 = ld3(FR_POS(sm, L, f1)) + mulM(FR_MAT(sm, L, f1), ld3(D.site_lpos + 3 * s1));
+    float wlen = -1.f; f3 w0 = p0, w1 = p1;
+    if (g >= 0) {
+      const int fg = D.geom_frame[g], sid = D.unit_side[u];
+      const f3 gpos = ld3(FR_POS(sm, L, fg)) + mulM(FR_MAT(sm, L, fg), ld3(D.geom_lpos + 3 * g));
+      float gm[9]; mulMM(gm, FR_MAT(sm, L, fg), D.geom_lmat + 9 * g);
+      f3 side = mk3(0.f, 0.f, 0.f);
+      if (sid >= 0) { const int fs = D.site_frame[sid]; side = ld3(FR_POS(sm, L, fs)) + mulM(FR_MAT(sm, L, fs), ld3(D.site_lpos + 3 * sid)); }
+      wlen = wrapGeom(p0, p1, gpos, gm, D.unit_radius[u], D.unit_type[u], sid >= 0, side, &w0, &w1);
+    }
+    const int sl0 = D.unit_slot[2 * u], sl1 = D.unit_slot[2 * u + 1];
+    float len;
+    if (wlen < 0.f) {
+      const f3 dif = p1 - p0; const float n = norm3(dif);
+      len = n;
+      if (sl0 >= 0) { st3(sm + L.slots + 6 * sl0, p0); st3(sm + L.slots + 6 * sl0 + 3, n > MINVAL ? dif * (1.f / n) : mk3(0.f, 0.f, 0.f)); }
+    } else {
+      const f3 d0 = w0 - p0, d1 = p1 - w1; const float n0 = norm3(d0), n1 = norm3(d1);
+      len = n0 + wlen + n1;
+      if (sl0 >= 0) { st3(sm + L.slots + 6 * sl0, p0); st3(sm + L.slots + 6 * sl0 + 3, n0 > MINVAL ? d0 * (1.f / n0) : mk3(0.f, 0.f, 0.f)); }
+      if (sl1 >= 0) { st3(sm + L.slots + 6 * sl1, w1); st3(sm + L.slots + 6 * sl1 + 3, n1 > MINVAL ? d1 * (1.f / n1) : mk3(0.f, 0.f, 0.f)); }
+    }
+    sm[L.ulen + u] = len / D.unit_div[u];
+    sm[L.uwrap + u] = wlen < 0.f ? 0.f : 1.f;
+  }
+  // #pragma unroll 1
+  for (int n = 0; n < D.nnz; n++) {
+    float acc = 0.f;
+    // #pragma unroll 1
+    for (int e = D.nz_estart[n]; e < D.nz_estart[n + 1]; e++) {
+      const int kind = D.ent_kind[e];
+      if (kind != ENT_ALWAYS) {
+        const bool wrapped = sm[L.uwrap + D.ent_unit[e]] != 0.f;
+        if ((kind == ENT_WRAP) != wrapped) continue;
+      }
+      const int i = D.ent_dof[e], sl = D.ent_slot[e];
+      const f3 p = ld3(sm + L.slots + 6 * sl), dir = ld3(sm + L.slots + 6 * sl + 3);
+      const f3 com = ld3(sm + L.rootcom + 3 * D.fr_root[D.dof_frame[i]]);
+      auto cd = sm + L.cdof + 6 * i;
+      acc += D.ent_scale[e] * (dot(ld3(cd), cross(p - com, dir)) + dot(ld3(cd + 3), dir));
+    }
+    sm[L.tenJ + n] = acc;
+  }
+  // #pragma unroll 1
+  for (int t = 0; t < D.nten; t++) {
+    float acc = 0.f;
+    // #pragma unroll 1
+    for (int u = D.ten_ustart[t]; u < D.ten_ustart[t + 1]; u++) acc += sm[L.ulen + u];
+    sm[L.tenlen + t] = acc;
+  }
+  void* tl = F.p[MYO_F_TEN_LENGTH]; void* tj = F.p[MYO_F_TEN_J];
+  if (tl) for (int t = 0; t < D.nten; t++) OUTF(tl, t) = sm[L.tenlen + t];
+  if (tj) {
+    // #pragma unroll 1
+    for (int t = 0; t < D.nten; t++) {   // dense row = zeros with the sparse entries (sorted by dof) merged in
+      int k = D.ten_nzstart[t];
+      const int kend = D.ten_nzstart[t + 1];
+      // #pragma unroll 1
+      for (int i = 0; i < D.nv; i++) {
+        float v = 0.f;
+        if (k < kend && D.nz_dof[k] == i) { v = sm[L.tenJ + k]; k++; }
+        OUTF(tj, t * D.nv + i) = v;
+      }
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------ inertia: mj_crb, mj_factorM, mj_solveM
+// sparse L^T D L in place over the dof-tree pattern (row i: entries M[i, i], M[i, parent(i)], ... at dof_Madr[i] + s)
+__device__ __noinline__ void factorLDL(int slot, SP LD, SP dinv) {
+  const DevModel& D = tP[slot].D;
+  const int nv = D.nv;
+  // #pragma unroll 1
+  for (int pos = 0; pos < nv; pos++) {
+    const int k = nv - 1 - pos, akk = D.dof_Madr[k];
+    const float inv = 1.f / LD[akk];
+    // #pragma unroll 1
+    for (int o = D.ldl_start[pos]; o < D.ldl_start[pos + 1]; o++) LD[D.ldl_dst[o]] -= LD[D.ldl_a[o]] * LD[D.ldl_b[o]] * inv;
+    const int d = D.dof_rowlen[k];
+    // #pragma unroll 1
+    for (int s = 1; s < d; s++) LD[akk + s] *= inv;
+    dinv[k] = inv;
+  }
+}
+// x <- (L^T D L)^-1 x
+__device__ __noinline__ void solveLDL(int slot, SP LD, SP dinv, SP x) {
+  const DevModel& D = tP[slot].D;
+  const int nv = D.nv;
+  // x <- L^-T x : column sweep from the last dof, scattering into the ancestors
+  // #pragma unroll 1
+  for (int i = nv - 1; i >= 0; i--) {
+    const int a = D.dof_Madr[i], d = D.dof_rowlen[i];
+    const float xi = x[i];
+    // #pragma unroll 1
+    for (int s = 1; s < d; s++) { const int j = D.M_col[a + s]; x[j] = fmaf(-LD[a + s], xi, x[j]); }
+  }
+  // #pragma unroll 1
+  for (int i = 0; i < nv; i++) x[i] *= dinv[i];
+  // x <- L^-1 x : rows in increasing order, gathering from the ancestors
+  // #pragma unroll 1
+  for (int i = 0; i < nv; i++) {
+    const int a = D.dof_Madr[i], d = D.dof_rowlen[i];
+    float acc = x[i];
+    // #pragma unroll 1
+    for (int s = 1; s < d; s++) acc = fmaf(-LD[a + s], x[D.M_col[a + s]], acc);
+    x[i] = acc;
+  }
+}
+__device__ __noinline__ void inertia(int slot, int fslot, SP sm, World W) {
+  const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L; const FieldPtrs& F = tP[fslot].F;
+  const int nv = D.nv;
+  // composite inertia of each frame's subtree: backward sweep over the depth-first frame order
+  // #pragma unroll 1
+  for (int i = 0; i < 10 * D.nframe; i++) sm[L.crb + i] = sm[L.cinert + i];
+  // #pragma unroll 1
+  for (int f = D.nframe - 1; f >= 1; f--) {
+    const int p = D.fr_parent[f];
+    if (p > 0)
+#pragma unroll
+      for (int k = 0; k < 10; k++) sm[L.crb + 10 * p + k] += sm[L.crb + 10 * f + k];
+  }
+  // #pragma unroll 1
+  for (int i = 0; i < nv; i++) {
+    float f6[6];
+    inertMulVec(f6, sm + L.crb + 10 * D.dof_frame[i], sm + L.cdof + 6 * i);
+    const int a = D.dof_Madr[i], d = D.dof_rowlen[i];
+    // #pragma unroll 1
+    for (int s = 0; s < d; s++) {
+      auto c = sm + L.cdof + 6 * D.M_col[a + s];
+      float v = c[0] * f6[0] + c[1] * f6[1] + c[2] * f6[2] + c[3] * f6[3] + c[4] * f6[4] + c[5] * f6[5];
+      if (s == 0) v += D.dof_armature[i];
+      sm[L.qM + a + s] = v; sm[L.qLD + a + s] = v;
+    }
+  }
+  factorLDL(slot, sm + L.qLD, sm + L.qLDinv);
+  void* qMo = F.p[MYO_F_QM]; void* qLDo = F.p[MYO_F_QLD]; void* qdi = F.p[MYO_F_QLDIAGINV];
+  if (qMo || qLDo) {
+    // #pragma unroll 1
+    for (int i = 0; i < nv * nv; i++) { if (qMo) OUTF(qMo, i) = 0.f; if (qLDo) OUTF(qLDo, i) = 0.f; }
+    // #pragma unroll 1
+    for (int e = 0; e < D.nM; e++) {
+      const int r = D.M_row[e], c = D.M_col[e];
+      if (qMo) { OUTF(qMo, r * nv + c) = sm[L.qM + e]; OUTF(qMo, c * nv + r) = sm[L.qM + e]; }
+      if (qLDo) OUTF(qLDo, r * nv + c) = sm[L.qLD + e];
+    }
+  }
+  if (qdi) for (int i = 0; i < nv; i++) OUTF(qdi, i) = sm[L.qLDinv + i];
+}
+
+// ------------------------------------------------------------------------------------------ mj_fwdVelocity
+__device__ __noinline__ void velocity(int slot, int fslot, SP sm, World W) {
+  const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L; const FieldPtrs& F = tP[fslot].F;
+  const int nv = D.nv;
+  auto qvel = sm + L.qvel;
+  // #pragma unroll 1
+  for (int t = 0; t < D.nten; t++) {
+    float acc = 0.f;
+    // #pragma unroll 1
+    for (int n = D.ten_nzstart[t]; n < D.ten_nzstart[t + 1]; n++) acc = fmaf(sm[L.tenJ + n], qvel[D.nz_dof[n]], acc);
+    sm[L.tenvel + t] = acc;
+  }
+  // body velocities down the tree (all motion axes are expressed about the tree's centre of mass), with
+  // cdof_dot = cvel(before this dof) x cdof on the way
+  const bool grav = !(D.disableflags & DSBL_GRAVITY);
+  // #pragma unroll 1
+  for (int k = 0; k < 6; k++) { sm[L.cvel + k] = 0.f; sm[L.cacc + k] = 0.f; }
+  // #pragma unroll 1
+  for (int f = 1; f < D.nframe; f++) {
+    const int p = D.fr_parent[f];
+    float v[6], a6[6];
+#pragma unroll
+    for (int k = 0; k < 6; k++) v[k] = sm[L.cvel + 6 * p + k];
+    if (p == 0) { a6[0] = a6[1] = a6[2] = 0.f; a6[3] = grav ? -D.gravity[0] : 0.f; a6[4] = grav ? -D.gravity[1] : 0.f; a6[5] = grav ? -D.gravity[2] : 0.f; }
+    else {
+#pragma unroll
+      for (int k = 0; k < 6; k++) a6[k] = sm[L.cacc + 6 * p + k];
+    }
+    const int da = D.fr_dofadr[f], dn = D.fr_dofnum[f];
+    const bool isfree = D.jnt_type[D.fr_jntadr[f]] == JNT_FREE;
+    float vstart[6];
+#pragma unroll
+    for (int k = 0; k < 6; k++) vstart[k] = v[k];
+    // #pragma unroll 1
+    for (int i = da; i < da + dn; i++) {
+      auto cd = sm + L.cdof + 6 * i;
+      auto cdd = sm + L.cdof_dot + 6 * i;
+      const int pc = D.dof_prevcount[i];
+      // free joint: translations have zero cdof_dot, rotations use the velocity after the translational dofs
+      if (pc < 0) { for (int k = 0; k < 6; k++) cdd[k] = 0.f; }
+      else if (isfree) {
+        if (i == da + 3) for (int k = 0; k < 6; k++) vstart[k] = v[k];
+        crossMotion(cdd, vstart, cd);
+      } else crossMotion(cdd, v, cd);
+      const float qv = qvel[i];
+#pragma unroll
+      for (int k = 0; k < 6; k++) { v[k] = fmaf(cd[k], qv, v[k]); a6[k] = fmaf(cdd[k], qv, a6[k]); }
+    }
+#pragma unroll
+    for (int k = 0; k < 6; k++) { sm[L.cvel + 6 * f + k] = v[k]; sm[L.cacc + 6 * f + k] = a6[k]; }
+  }
+  // body forces cfrc = I a + v x* (I v), accumulated up the tree; bias = cdof . cfrc(subtree)
+  auto cfrc = sm + L.cacc;   // in place: cacc[f] becomes the body force, a frame's acceleration is not needed after it
+  // #pragma unroll 1
+  for (int f = 0; f < D.nframe; f++) {
+    auto o = cfrc + 6 * f;
+    if (f == 0) { for (int k = 0; k < 6; k++) o[k] = 0.f; continue; }
+    float Ia[6], Iv[6], cf[6];
+    inertMulVec(Ia, sm + L.cinert + 10 * f, sm + L.cacc + 6 * f);
+    inertMulVec(Iv, sm + L.cinert + 10 * f, sm + L.cvel + 6 * f);
+    crossForce(cf, sm + L.cvel + 6 * f, Iv);
+#pragma unroll
+    for (int k = 0; k < 6; k++) o[k] = Ia[k] + cf[k];
+  }
+  // #pragma unroll 1
+  for (int f = D.nframe - 1; f >= 1; f--) {
+    const int p = D.fr_parent[f];
+    if (p > 0)
+#pragma unroll
+      for (int k = 0; k < 6; k++) cfrc[6 * p + k] += cfrc[6 * f + k];
+  }
+  const bool passive_on = !(D.disableflags & DSBL_PASSIVE);
+  void* osp = F.p[MYO_F_QFRC_SPRING]; void* odm = F.p[MYO_F_QFRC_DAMPER]; void* ops = F.p[MYO_F_QFRC_PASSIVE]; void* obi = F.p[MYO_F_QFRC_BIAS];
+  // #pragma unroll 1
+  for (int i = 0; i < nv; i++) {
+    auto acc = cfrc + 6 * D.dof_frame[i];
+    auto cd = sm + L.cdof + 6 * i;
+    const float bias = cd[0] * acc[0] + cd[1] * acc[1] + cd[2] * acc[2] + cd[3] * acc[3] + cd[4] * acc[4] + cd[5] * acc[5];
+    sm[L.bias + i] = bias;
+    float spring = 0.f, damper = 0.f;
+    if (passive_on) {
+      const int j = D.dof_jnt[i];
+      const float k = D.jnt_stiffness[j];
+      if (k != 0.f && D.jnt_type[j] >= JNT_SLIDE) spring = -k * (sm[L.qpos + D.jnt_qposadr[j]] - D.qpos_spring[D.jnt_qposadr[j]]);
+      damper = -D.dof_damping[i] * qvel[i];
+      if (D.any_tendon_passive)
+        // #pragma unroll 1
+        for (int c = D.col_start[i]; c < D.col_start[i + 1]; c++) {
+          const int n = D.col_nz[c], t = D.nz_tendon[n];
+          const float ks = D.ten_stiffness[t], kd = D.ten_damping[t], len = sm[L.tenlen + t];
+          if (ks > 0.f) {
+            const float lo = D.ten_lengthspring[2 * t], hi = D.ten_lengthspring[2 * t + 1];
+            const float fs = len > hi ? ks * (hi - len) : (len < lo ? ks * (lo - len) : 0.f);
+            spring += sm[L.tenJ + n] * fs;
+          }
+          if (kd > 0.f) damper -= kd * sm[L.tenvel + t] * sm[L.tenJ + n];
+        }
+    }
+    sm[L.passive + i] = spring + damper;
+    if (osp) OUTF(osp, i) = spring;
+    if (odm) OUTF(odm, i) = damper;
+    if (ops) OUTF(ops, i) = spring + damper;
+    if (obi) OUTF(obi, i) = bias;
+  }
+  void* o;
+  if ((o = F.p[MYO_F_TEN_VELOCITY])) for (int t = 0; t < D.nten; t++) OUTF(o, t) = sm[L.tenvel + t];
+  if ((o = F.p[MYO_F_CDOF_DOT])) for (int i = 0; i < 6 * nv; i++) OUTF(o, i) = sm[L.cdof_dot + i];
+  if ((o = F.p[MYO_F_CVEL])) for (int b = 0; b < D.nbody; b++) for (int k = 0; k < 6; k++) OUTF(o, 6 * b + k) = sm[L.cvel + 6 * D.body_frame[b] + k];
+}
+// ------------------------------------------------------------------------------------------ mj_fwdActuation
+__device__ __forceinline__ float muscleFL(float Ln, float lmin, float lmax) {
+  if (Ln < lmin || Ln > lmax) return 0.f;
+  const float a = 0.5f * (lmin + 1.f), b = 0.5f * (1.f + lmax);
+  float x;
+  if (Ln <= a) { x = (Ln - lmin) / fmaxf(MINVAL, a - lmin); return 0.5f * x * x; }
+  if (Ln <= 1.f) { x = (1.f - Ln) / fmaxf(MINVAL, 1.f - a); return 1.f - 0.5f * x * x; }
+  if (Ln <= b) { x = (Ln - 1.f) / fmaxf(MINVAL, b - 1.f); return 1.f - 0.5f * x * x; }
+  x = (lmax - Ln) / fmaxf(MINVAL, lmax - b);
+  return 0.5f * x * x;
+}
+__device__ __noinline__ void muscleGainBias(float len, float vel, const float* lr, float acc0, const float* prm, float* gain, float* bias) {
+  const float r0 = prm[0], r1 = prm[1], scale = prm[3], lmin = prm[4], lmax = prm[5], vmax = prm[6], fpmax = prm[7], fvmax = prm[8];
+  float force = prm[2];
+  if (force < 0.f) force = scale / fmaxf(MINVAL, acc0);
+  const float L0 = (lr[1] - lr[0]) / fmaxf(MINVAL, r1 - r0);
+  const float Ln = r0 + (len - lr[0]) / fmaxf(MINVAL, L0);
+  const float V = vel / fmaxf(MINVAL, L0 * vmax);
+  const float FL = muscleFL(Ln, lmin, lmax);
+  const float y = fvmax - 1.f;
+  float FV;
+  if (V <= -1.f) FV = 0.f;
+  else if (V <= 0.f) FV = (V + 1.f) * (V + 1.f);
+  else if (V <= y) FV = fvmax - (y - V) * (y - V) / fmaxf(MINVAL, y);
+  else FV = fvmax;
+  *gain = -force * FL * FV;
+  const float b = 0.5f * (1.f + lmax);
+  if (Ln <= 1.f) *bias = 0.f;
+  else if (Ln <= b) { const float x = (Ln - 1.f) / fmaxf(MINVAL, b - 1.f); *bias = -force * fpmax * 0.5f * x * x; }
+  else { const float x = (Ln - b) / fmaxf(MINVAL, b - 1.f); *bias = -force * fpmax * (0.5f + x); }
+}
+__device__ __noinline__ void actuation(int slot, int fslot, SP sm, World W) {
+  const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L; const FieldPtrs& F = tP[fslot].F;
+  const int nu = D.nu, nv = D.nv;
+  const bool on = !(D.disableflags & DSBL_ACTUATION);
+  void* olen = F.p[MYO_F_ACTUATOR_LENGTH]; void* ovel = F.p[MYO_F_ACTUATOR_VELOCITY]; void* ofrc = F.p[MYO_F_ACTUATOR_FORCE];
+  void* odot = F.p[MYO_F_ACT_DOT];
+  // #pragma unroll 1
+  for (int t = 0; t < D.nten; t++) sm[L.tforce + t] = 0.f;
+  // #pragma unroll 1
+  for (int i = 0; i < nv; i++) sm[L.qfrc_act + i] = 0.f;
+  // #pragma unroll 1
+  for (int i = 0; i < nu; i++) {
+    const int id = D.act_trnid[i];
+    const float gear = D.act_gear[i];
+    const bool ten = D.act_trntype[i] == 3;
+    float len, vel;
+    if (ten) { len = gear * sm[L.tenlen + id]; vel = gear * sm[L.tenvel + id]; }
+    else { len = gear * sm[L.qpos + D.jnt_qposadr[id]]; vel = gear * sm[L.qvel + D.jnt_dofadr[id]]; }
+    float force = 0.f, adot = 0.f;
+    const int aa = D.act_actadr[i];
+    if (on) {
+      float c = sm[L.ctrl + i];
+      const int fl = D.act_flags[i];
+      if ((fl & ACT_CTRLLIMITED) && !(D.disableflags & DSBL_CLAMPCTRL)) c = clipf(c, D.act_ctrlrange[2 * i], D.act_ctrlrange[2 * i + 1]);
+      float a = c;
+      if (aa >= 0) {
+        a = sm[L.act + aa];
+        auto dp = D.act_dynprm + 3 * i;
+        const int dt = D.act_dyntype[i];
+        if (dt == DYN_INTEGRATOR) adot = c;
+        else if (dt == DYN_FILTER || dt == DYN_FILTEREXACT) adot = (c - a) / fmaxf(MINVAL, dp[0]);
+        else if (dt == DYN_MUSCLE) {
+          const float cc = clipf(c, 0.f, 1.f), ac = clipf(a, 0.f, 1.f);
+          const float ta = dp[0] * (0.5f + 1.5f * ac), td = dp[1] / (0.5f + 1.5f * ac), dctrl = cc - a;
+          float tau;
+          if (dp[2] < MINVAL) tau = dctrl > 0.f ? ta : td;
+          else { const float x = clipf(dctrl / dp[2] + 0.5f, 0.f, 1.f); tau = td + (ta - td) * (x * x * x * (x * (6.f * x - 15.f) + 10.f)); }
+          adot = dctrl / fmaxf(MINVAL, tau);
+        }
+      }
+      auto gp = D.act_gainprm + 9 * i; auto bp = D.act_biasprm + 9 * i;
+      float gain = 0.f, bias = 0.f, tmp;
+      const int gt = D.act_gaintype[i], bt = D.act_biastype[i];
+      if (gt == GAIN_MUSCLE && bt == BIAS_MUSCLE && D.act_same_prm[i]) muscleGainBias(len, vel, D.act_lengthrange + 2 * i, D.act_acc0[i], gp, &gain, &bias);
+      else {
+        if (gt == GAIN_FIXED) gain = gp[0];
+        else if (gt == GAIN_AFFINE) gain = gp[0] + gp[1] * len + gp[2] * vel;
+        else muscleGainBias(len, vel, D.act_lengthrange + 2 * i, D.act_acc0[i], gp, &gain, &tmp);
+        if (bt == BIAS_AFFINE) bias = bp[0] + bp[1] * len + bp[2] * vel;
+        else if (bt == BIAS_MUSCLE) muscleGainBias(len, vel, D.act_lengthrange + 2 * i, D.act_acc0[i], bp, &tmp, &bias);
+      }
+      force = gain * a + bias;
+      if (fl & ACT_FORCELIMITED) force = clipf(force, D.act_forcerange[2 * i], D.act_forcerange[2 * i + 1]);
+    }
+    sm[L.actforce + i] = force;
+    if (aa >= 0) { sm[L.actdot + aa] = adot; if (odot) OUTF(odot, aa) = adot; }
+    if (ten) sm[L.tforce + id] += gear * force; else sm[L.qfrc_act + D.jnt_dofadr[id]] += gear * force;
+    if (olen) OUTF(olen, i) = len;
+    if (ovel) OUTF(ovel, i) = vel;
+    if (ofrc) OUTF(ofrc, i) = force;
+  }
+  // qfrc_actuator = moment^T force through the sparse tendon rows
+  // #pragma unroll 1
+  for (int t = 0; t < D.nten; t++) {
+    const float tf = sm[L.tforce + t];
+    if (tf == 0.f) continue;
+    // #pragma unroll 1
+    for (int n = D.ten_nzstart[t]; n < D.ten_nzstart[t + 1]; n++) sm[L.qfrc_act + D.nz_dof[n]] = fmaf(sm[L.tenJ + n], tf, sm[L.qfrc_act + D.nz_dof[n]]);
+  }
+  // #pragma unroll 1
+  for (int i = 0; i < nv; i++) {
+    const float sf = sm[L.passive + i] - sm[L.bias + i] + sm[L.qfrc_act + i];
+    sm[L.smooth + i] = sf; sm[L.qacc_smooth + i] = sf;
+  }
+  solveLDL(slot, sm + L.qLD, sm + L.qLDinv, sm + L.qacc_smooth);
+  void* o;
+  if ((o = F.p[MYO_F_QFRC_ACTUATOR])) for (int i = 0; i < nv; i++) OUTF(o, i) = sm[L.qfrc_act + i];
+  if ((o = F.p[MYO_F_QFRC_SMOOTH])) for (int i = 0; i < nv; i++) OUTF(o, i) = sm[L.smooth + i];
+  if ((o = F.p[MYO_F_QACC_SMOOTH])) for (int i = 0; i < nv; i++) OUTF(o, i) = sm[L.qacc_smooth + i];
+  if ((o = F.p[MYO_F_ACTUATOR_MOMENT])) {
+    // #pragma unroll 1
+    for (int a = 0; a < nu; a++) {   // dense row = the tendon's sparse row scaled by the gear
+      const int id = D.act_trnid[a];
+      const bool ten = D.act_trntype[a] == 3;
+      int k = ten ? D.ten_nzstart[id] : 0;
+      const int kend = ten ? D.ten_nzstart[id + 1] : 0;
+      const int jd = ten ? -1 : D.jnt_dofadr[id];
+      const float gear = D.act_gear[a];
+      // #pragma unroll 1
+      for (int i = 0; i < nv; i++) {
+        float v = 0.f;
+        if (k < kend && D.nz_dof[k] == i) { v = gear * sm[L.tenJ + k]; k++; }
+        if (i == jd) v = gear;
+        OUTF(o, a * nv + i) = v;
+      }
+    }
+  }
+}
+// ------------------------------------------------------------------------------------------ collision
+// The convex narrow phase (Minkowski portal refinement on B - A) runs in float64: its result is defined by an
+// iteration with a 1e-6 stopping rule, and in float32 the portal degenerates near convergence (contact points of
+// ellipsoids moved by millimetres).  Few pairs reach it per world and B200 runs FP64 at half the FP32 rate.
+struct d3 { double x, y, z; };
+__device__ __forceinline__ d3 mkd(double x, double y, double z) { d3 r; r.x = x; r.y = y; r.z = z; return r; }
+__device__ __forceinline__ d3 operator+(d3 a, d3 b) { return mkd(a.x + b.x, a.y + b.y, a.z + b.z); }
+__device__ __forceinline__ d3 operator-(d3 a, d3 b) { return mkd(a.x - b.x, a.y - b.y, a.z - b.z); }
+__device__ __forceinline__ d3 operator*(d3 a, double s) { return mkd(a.x * s, a.y * s, a.z * s); }
+__device__ __forceinline__ double dot(d3 a, d3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+__device__ __forceinline__ d3 cross(d3 a, d3 b) { return mkd(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x); }
+__device__ __forceinline__ double norm3(d3 a) { return sqrt(dot(a, a)); }
+__device__ __forceinline__ d3 unit3(d3 a) { const double n = norm3(a); return n < 1e-15 ? mkd(1.0, 0.0, 0.0) : a * (1.0 / n); }
+struct Shape { int type; d3 pos; SP mat; d3 size; double margin; };
+__device__ __noinline__ d3 supportPt(const Shape& s, d3 dir) {
+  auto R = s.mat;
+  const d3 d = mkd(R[0] * dir.x + R[3] * dir.y + R[6] * dir.z, R[1] * dir.x + R[4] * dir.y + R[7] * dir.z, R[2] * dir.x + R[5] * dir.y + R[8] * dir.z);
+  d3 r = mkd(0.0, 0.0, 0.0);
+  switch (s.type) {
+    case G_SPHERE: r = d * s.size.x; break;
+    case G_CAPSULE: r = d * s.size.x; r.z += d.z >= 0.0 ? s.size.y : -s.size.y; break;
+    case G_ELLIPSOID: {
+      const d3 t = mkd(s.size.x * s.size.x * d.x, s.size.y * s.size.y * d.y, s.size.z * s.size.z * d.z);
+      r = t * (1.0 / sqrt(fmax(1e-30, t.x * d.x + t.y * d.y + t.z * d.z)));
+    } break;
+    case G_CYLINDER: {
+      const double n = sqrt(d.x * d.x + d.y * d.y);
+      if (n > 1e-12) { r.x = s.size.x * d.x / n; r.y = s.size.x * d.y / n; }
+      r.z = d.z >= 0.0 ? s.size.y : -s.size.y;
+    } break;
+    case G_BOX: r = mkd(d.x >= 0.0 ? s.size.x : -s.size.x, d.y >= 0.0 ? s.size.y : -s.size.y, d.z >= 0.0 ? s.size.z : -s.size.z); break;
+    default: break;
+  }
+  return mkd(R[0] * r.x + R[1] * r.y + R[2] * r.z, R[3] * r.x + R[4] * r.y + R[5] * r.z, R[6] * r.x + R[7] * r.y + R[8] * r.z) + s.pos + dir * s.margin;
+}
+struct Sup { d3 v, a, b; };
+__device__ __noinline__ Sup mprSup(const Shape& A, const Shape& B, d3 d) {
+  Sup s; s.a = supportPt(A, d * -1.0); s.b = supportPt(B, d); s.v = s.b - s.a; return s;
+}
+__device__ __noinline__ bool mprPenetration(const Shape& A, const Shape& B, double tol, int maxit, double* depth, d3* nrm, d3* pos) {
+  d3 v0 = B.pos - A.pos;
+  if (norm3(v0) < 1e-12) v0 = mkd(1e-5, 0.0, 0.0);
+  d3 dir = unit3(v0 * -1.0);
+  Sup s1 = mprSup(A, B, dir);
+  if (dot(s1.v, dir) <= 0.0) return false;
+  dir = cross(s1.v, v0);
+  if (norm3(dir) < 1e-12 * fmax(1.0, norm3(s1.v) * norm3(v0))) {
+    const d3 n = unit3(s1.v - v0);
+    *depth = dot(s1.v, n); *nrm = n * -1.0; *pos = (s1.a + s1.b) * 0.5;
+    return true;
+  }
+  dir = unit3(dir);
+  Sup s2 = mprSup(A, B, dir);
+  if (dot(s2.v, dir) <= 0.0) return false;
+  dir = unit3(cross(s1.v - v0, s2.v - v0));
+  if (dot(dir, v0) > 0.0) { Sup t = s1; s1 = s2; s2 = t; dir = dir * -1.0; }
+  Sup s3;
+  // #pragma unroll 1
+  for (int it = 0;; it++) {
+    if (it > maxit) return false;
+    s3 = mprSup(A, B, dir);
+    if (dot(s3.v, dir) <= 0.0) return false;
+    if (dot(cross(s1.v, s3.v), v0) < 0.0) { s2 = s3; dir = unit3(cross(s1.v - v0, s3.v - v0)); continue; }
+    if (dot(cross(s3.v, s2.v), v0) < 0.0) { s1 = s3; dir = unit3(cross(s3.v - v0, s2.v - v0)); continue; }
+    break;
+  }
+  bool hit = false;
+  // #pragma unroll 1
+  for (int it = 0;; it++) {
+    dir = unit3(cross(s2.v - s1.v, s3.v - s1.v));
+    if (dot(dir, s1.v) >= 0.0) hit = true;
+    const Sup s4 = mprSup(A, B, dir);
+    if (dot(s4.v, dir) < 0.0 && !hit) return false;
+    const double adv = fmin(fmin(dot(s4.v - s1.v, dir), dot(s4.v - s2.v, dir)), dot(s4.v - s3.v, dir));
+    if (adv <= tol || it >= maxit) {
+      if (!hit) return false;
+      const double d = dot(dir, s1.v);
+      const d3 p = dir * d, e0 = s2.v - s1.v, e1 = s3.v - s1.v, e2 = p - s1.v;
+      const double d00 = dot(e0, e0), d01 = dot(e0, e1), d11 = dot(e1, e1), d20 = dot(e2, e0), d21 = dot(e2, e1);
+      const double den = d00 * d11 - d01 * d01;
+      double b1 = 1.0, b2 = 0.0, b3 = 0.0;
+      if (fabs(den) > 1e-30) { b2 = (d11 * d20 - d01 * d21) / den; b3 = (d00 * d21 - d01 * d20) / den; b1 = 1.0 - b2 - b3; }
+      b1 = fmin(fmax(b1, 0.0), 1.0); b2 = fmin(fmax(b2, 0.0), 1.0); b3 = fmin(fmax(b3, 0.0), 1.0);
+      const double bs = 1.0 / fmax(1e-30, b1 + b2 + b3);
+      const d3 pa = (s1.a * b1 + s2.a * b2 + s3.a * b3) * bs, pb = (s1.b * b1 + s2.b * b2 + s3.b * b3) * bs;
+      *depth = d; *nrm = dir * -1.0; *pos = (pa + pb) * 0.5;
+      return true;
+    }
+    const d3 c = cross(s4.v, v0);
+    if (dot(s1.v, c) > 0.0) { if (dot(s2.v, c) > 0.0) s1 = s4; else s3 = s4; }
+    else { if (dot(s3.v, c) > 0.0) s2 = s4; else s1 = s4; }
+  }
+}
+struct Hit { float dist; f3 pos, nrm; };
+__device__ __forceinline__ Hit sphereSphere(f3 c1, float r1, f3 c2, float r2) {
+  const f3 d = c2 - c1; const float n = norm3(d);
+  Hit h; h.nrm = n < MINVAL ? mk3(1.f, 0.f, 0.f) : d * (1.f / n);
+  h.dist = n - r1 - r2; h.pos = c1 + h.nrm * (r1 + 0.5f * h.dist);
+  return h;
+}
+// narrow phase for one candidate pair; returns the number of contacts (0..2) with dist < margin
+__device__ __noinline__ int collidePair(int slot, SP sm, int pr, Hit* h) {
+  const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
+  const int c1 = D.pair_cg1[pr], c2 = D.pair_cg2[pr];
+  const int t1 = D.cg_type[c1], t2 = D.cg_type[c2];
+  const float margin = D.pair_prm[16 * pr];
+  auto P1 = sm + L.cgpose + 12 * c1; auto P2 = sm + L.cgpose + 12 * c2;
+  const f3 p1 = ld3(P1), p2 = ld3(P2);
+  const SP R1 = P1 + 3, R2 = P2 + 3;
+  const f3 sz1 = ld3(D.cg_size + 3 * c1), sz2 = ld3(D.cg_size + 3 * c2);
+  const f3 ax1 = mk3(R1[2], R1[5], R1[8]), ax2 = mk3(R2[2], R2[5], R2[8]);
+  int n = 0;
+  if (t1 == G_PLANE) {
+    if (dot(p2 - p1, ax1) > D.cg_rbound[c2] + margin) return 0;
+    if (t2 == G_SPHERE || t2 == G_CAPSULE) {
+      const int cnt = t2 == G_SPHERE ? 1 : 2;
+      // #pragma unroll 1
+      for (int k = 0; k < cnt; k++) {
+        const f3 c = t2 == G_SPHERE ? p2 : (k == 0 ? p2 + ax2 * sz2.y : p2 - ax2 * sz2.y);
+        const float dist = dot(c - p1, ax1) - sz2.x;
+        if (dist < margin) { h[n].dist = dist; h[n].pos = c - ax1 * (sz2.x + 0.5f * dist); h[n].nrm = ax1; n++; }
+      }
+    } else {
+      Shape s; s.type = t2; s.pos = mkd(p2.x, p2.y, p2.z); s.mat = R2; s.size = mkd(sz2.x, sz2.y, sz2.z); s.margin = 0.0;
+      const d3 spd = supportPt(s, mkd(-ax1.x, -ax1.y, -ax1.z));
+      const f3 sp = mk3((float)spd.x, (float)spd.y, (float)spd.z);
+      const float dist = (float)((spd.x - p1.x) * ax1.x + (spd.y - p1.y) * ax1.y + (spd.z - p1.z) * ax1.z);
+      if (dist < margin) { h[0].dist = dist; h[0].pos = sp - ax1 * (0.5f * dist); h[0].nrm = ax1; n = 1; }
+    }
+    return n;
+  }
+  if (norm3(p2 - p1) > D.cg_rbound[c1] + D.cg_rbound[c2] + margin) return 0;
+  if (t1 == G_SPHERE && t2 == G_SPHERE) h[0] = sphereSphere(p1, sz1.x, p2, sz2.x);
+  else if (t1 == G_SPHERE && t2 == G_CAPSULE) h[0] = sphereSphere(p1, sz1.x, p2 + ax2 * clipf(dot(p1 - p2, ax2), -sz2.y, sz2.y), sz2.x);
+  else if (t1 == G_CAPSULE && t2 == G_CAPSULE) {
+    const f3 a1 = ax1 * sz1.y, a2 = ax2 * sz2.y, dif = p1 - p2;
+    const float ma = dot(a1, a1), mb = -dot(a1, a2), mc = dot(a2, a2), u = -dot(a1, dif), v = dot(a2, dif);
+    const float det = ma * mc - mb * mb;
+    float x1, x2;
+    if (fabsf(det) >= 1e-30f) {
+      x1 = (mc * u - mb * v) / det; x2 = (ma * v - mb * u) / det;
+      if (x1 > 1.f) { x1 = 1.f; x2 = (v - mb) / mc; } else if (x1 < -1.f) { x1 = -1.f; x2 = (v + mb) / mc; }
+      if (x2 > 1.f) { x2 = 1.f; x1 = clipf((u - mb) / ma, -1.f, 1.f); } else if (x2 < -1.f) { x2 = -1.f; x1 = clipf((u + mb) / ma, -1.f, 1.f); }
+    } else {
+      x1 = clipf(u / fmaxf(1e-30f, ma), -1.f, 1.f);
+      x2 = clipf((v - mb * x1) / fmaxf(1e-30f, mc), -1.f, 1.f);
+    }
+    h[0] = sphereSphere(p1 + a1 * x1, sz1.x, p2 + a2 * x2, sz2.x);
+  } else {
+    Shape A, B;
+    A.type = t1; A.pos = mkd(p1.x, p1.y, p1.z); A.mat = R1; A.size = mkd(sz1.x, sz1.y, sz1.z); A.margin = 0.5 * (double)margin;
+    B.type = t2; B.pos = mkd(p2.x, p2.y, p2.z); B.mat = R2; B.size = mkd(sz2.x, sz2.y, sz2.z); B.margin = 0.5 * (double)margin;
+    double depth; d3 nrm, pos;
+    if (!mprPenetration(A, B, 1e-6, 50, &depth, &nrm, &pos)) return 0;
+    h[0].dist = (float)((double)margin - depth); h[0].pos = mk3((float)pos.x, (float)pos.y, (float)pos.z);
+    h[0].nrm = mk3((float)nrm.x, (float)nrm.y, (float)nrm.z);
+  }
+  return h[0].dist < margin ? 1 : 0;
+}
+__device__ __forceinline__ void makeFrame(f3 n, f3* y, f3* z) {
+  f3 t = mk3(0.f, 0.f, 0.f);
+  if (n.y < 0.5f && n.y > -0.5f) t.y = 1.f; else t.z = 1.f;
+  t = unit3(t - n * dot(n, t));
+  *y = t; *z = cross(n, t);
+}
+// returns the number of contacts; contact record: dist, pos[3], normal[3], pair, efc_address, dim, spare[2]
+// Pass 1 (uniform over the warp): bounding-sphere / plane-distance filter over the static candidate-pair list, each
+// lane compacting ITS survivors.  Pass 2: lane-private survivor lists are walked in lock-step, so the narrow phase
+// runs max-over-lanes(#survivors) times instead of once per static pair; pair order (hence contact order) is kept.
+__device__ __noinline__ int collision(int slot, SP sm, int* status) {
+  const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
+  if (D.npair == 0) return 0;
+  // #pragma unroll 1
+  for (int c = 0; c < D.ncg; c++) {
+    const int f = D.cg_frame[c];
+    auto o = sm + L.cgpose + 12 * c;
+    st3(o, ld3(FR_POS(sm, L, f)) + mulM(FR_MAT(sm, L, f), ld3(D.cg_lpos + 3 * c)));
+    mulMM(o + 3, FR_MAT(sm, L, f), D.cg_lmat + 9 * c);
+  }
+  SPI cand = asInt(sm + L.cand);
+  int ncand = 0;
+  // #pragma unroll 1
+  for (int pr = 0; pr < D.npair; pr++) {
+    const int c1 = D.pair_cg1[pr], c2 = D.pair_cg2[pr];
+    auto P1 = sm + L.cgpose + 12 * c1; auto P2 = sm + L.cgpose + 12 * c2;
+    const f3 d = ld3(P2) - ld3(P1);
+    const float margin = D.pair_prm[16 * pr];
+    bool pass;
+    if (D.cg_type[c1] == G_PLANE) pass = !(d.x * P1[5] + d.y * P1[8] + d.z * P1[11] > D.cg_rbound[c2] + margin);
+    else { const float r = D.cg_rbound[c1] + D.cg_rbound[c2] + margin; pass = !(dot(d, d) > r * r); }
+    if (pass) cand[ncand++] = pr;
+  }
+  int ncon = 0;
+  // #pragma unroll 1
+  for (int k = 0; k < ncand; k++) {
+    const int pr = cand[k];
+    Hit h[2];
+    const int n = collidePair(slot, sm, pr, h);
+    // #pragma unroll 1
+    for (int q = 0; q < n; q++, ncon++) {
+      if (ncon >= D.nconmax) continue;
+      auto c = sm + L.con + 12 * ncon;
+      c[0] = h[q].dist; st3(c + 1, h[q].pos); st3(c + 4, h[q].nrm);
+      c[7] = __int_as_float(pr); c[8] = __int_as_float(-1); c[9] = __int_as_float(D.pair_dim[pr]);
+    }
+  }
+  if (ncon > D.nconmax) { *status |= MYO_WORLD_NCON_OVERFLOW; ncon = D.nconmax; }
+  return ncon;
+}
+
+// ------------------------------------------------------------------------------------------ constraints
+// Rows are never stored densely: a row is (type, id, coef) and its Jacobian is implied -- limit rows are 1-sparse,
+// equality rows 2-sparse, tendon-limit rows reuse the tendon's sparse moment-arm row, contact rows are +- combinations
+// of the contact's base rows (normal, 2 tangents, torsion) held in conJ.
+enum { E_D = 0, E_AREF, E_JAR, E_JV, E_FORCE, E_DESC0, E_COEF, E_DESC1, E_POS, E_MARGIN };
+#define EFC(k, r) sm[L.efc + (k) * D.njmax + (r)]
+#define EFCI(k, r) __float_as_int(sm[L.efc + (k) * D.njmax + (r)])
+
+__device__ __noinline__ float impedance(const float* si, float x) {  // si = sanitised solimp, x = |pos - margin|
+  const float dmin = si[0], dmax = si[1], width = si[2], mid = si[3], power = si[4];
+  if (dmin == dmax || width <= MINVAL) return 0.5f * (dmin + dmax);
+  x = x / width;
+  if (x >= 1.f) return dmax;
+  if (x <= 0.f) return dmin;
+  float y;
+  if (power == 1.f) y = x;
+  else if (x <= mid) y = pow_(x, power) / pow_(mid, power - 1.f);
+  else y = 1.f - pow_(1.f - x, power) / pow_(1.f - mid, power - 1.f);
+  return dmin + y * (dmax - dmin);
+}
+__device__ __noinline__ void setRow(int slot, SP sm, int r, int type, int id, float coef, int desc1,
+                                    float pos, float margin, float dA, const float* kb, float vel, float Rscale) {
+  const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
+  const float imp = impedance(kb + 2, fabsf(pos - margin));   // kb: K, B, solimp[5]
+  float R = fmaxf(MINVAL, (1.f - imp) * dA / imp);
+  if (Rscale > 0.f) R = fmaxf(MINVAL, Rscale * R);
+  EFC(E_D, r) = 1.f / R;
+  EFC(E_AREF, r) = -kb[1] * vel - kb[0] * imp * (pos - margin);
+  EFC(E_DESC0, r) = __int_as_float(type | (id << 2)); EFC(E_COEF, r) = coef; EFC(E_DESC1, r) = __int_as_float(desc1);
+  EFC(E_POS, r) = pos; EFC(E_MARGIN, r) = margin; EFC(E_FORCE, r) = 0.f;
+}
+// base-row products  out[b] = conJ[b] . x   for the nb*ncon contact base rows
+__device__ __noinline__ void baseMul(int slot, SP sm, int ncon, SP x, SP out) {
+  const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
+  const int nbr = D.maxbase * ncon, nv = D.nv;
+  // #pragma unroll 1
+  for (int b = 0; b < nbr; b++) {
+    auto J = sm + L.conJ + b * nv;
+    float acc = 0.f;
+    #pragma unroll 4
+    for (int k = 0; k < nv; k++) acc = fmaf(J[k], x[k], acc);
+    out[b] = acc;
+  }
+}
+// J_r . x for one efc row (bx = base products of x)
+__device__ __forceinline__ float rowMul(int slot, SP sm, int r, SP x, SP bx) {
+  const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
+  const int d0 = EFCI(E_DESC0, r), type = d0 & 3, id = d0 >> 2;
+  const float coef = EFC(E_COEF, r);
+  if (type == ROW_LIMJ) return coef * x[D.limj_dof[id]];
+  if (type == ROW_CON) { const int t = EFCI(E_DESC1, r); return bx[id] + (t >= 0 ? coef * bx[t] : 0.f); }
+  if (type == ROW_EQ) { const int d2 = D.eq_dof2[id]; return x[D.eq_dof1[id]] + (d2 >= 0 ? coef * x[d2] : 0.f); }
+  const int t = D.limt_ten[id];
+  float acc = 0.f;
+  // #pragma unroll 1
+  for (int n = D.ten_nzstart[t]; n < D.ten_nzstart[t + 1]; n++) acc += sm[L.tenJ + n] * x[D.nz_dof[n]];
+  return coef * acc;
+}
+
+__device__ __noinline__ int makeConstraint(int slot, SP sm, int ncon, int* status) {
+  const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
+  const int nv = D.nv, njmax = D.njmax;
+  auto qpos = sm + L.qpos; auto qvel = sm + L.qvel;
+  if (D.disableflags & DSBL_CONSTRAINT) return 0;
+  // ---- equality rows (always active)
+  // #pragma unroll 1
+  for (int e = 0; e < D.neq; e++) {
+    const int d1 = D.eq_dof1[e], d2 = D.eq_dof2[e], q1 = D.eq_q1[e], q2 = D.eq_q2[e];
+    auto dt = D.eq_data + 5 * e;
+    float pos, dpoly = 0.f, vel = qvel[d1];
+    if (d2 >= 0) {
+      const float x = qpos[q2] - D.qpos0[q2];
+      pos = qpos[q1] - D.qpos0[q1] - (dt[0] + x * (dt[1] + x * (dt[2] + x * (dt[3] + x * dt[4]))));
+      dpoly = dt[1] + x * (2.f * dt[2] + x * (3.f * dt[3] + x * 4.f * dt[4]));
+      vel -= dpoly * qvel[d2];
+    } else pos = qpos[q1] - D.qpos0[q1] - dt[0];
+    setRow(slot, sm, e, ROW_EQ, e, -dpoly, 0, pos, 0.f, D.eq_prm[8 * e + 7], D.eq_prm + 8 * e, vel, 0.f);
+  }
+  int nefc = D.neq;
+  // ---- joint limits, then tendon limits
+  const int nlim = D.nlimj + D.nlimt;
+  // #pragma unroll 1
+  for (int li = 0; li < nlim; li++) {
+    const bool isj = li < D.nlimj;
+    auto prm = isj ? D.limj_prm + 12 * li : D.limt_prm + 12 * (li - D.nlimj);
+    const float val = isj ? qpos[D.limj_q[li]] : sm[L.tenlen + D.limt_ten[li - D.nlimj]];
+    const float margin = prm[2], dlo = val - prm[0], dhi = prm[1] - val;
+    int r0 = -1, r1 = -1;
+    if (dlo < margin || dhi < margin) {
+      const float v = isj ? qvel[D.limj_dof[li]] : sm[L.tenvel + D.limt_ten[li - D.nlimj]];
+      const int id = isj ? li : li - D.nlimj, type = isj ? ROW_LIMJ : ROW_LIMT;
+      if (dlo < margin) { if (nefc < njmax) { r0 = nefc; setRow(slot, sm, nefc, type, id, 1.f, 0, dlo, margin, prm[10], prm + 3, v, 0.f); } nefc++; }
+      if (dhi < margin) { if (nefc < njmax) { r1 = nefc; setRow(slot, sm, nefc, type, id, -1.f, 0, dhi, margin, prm[10], prm + 3, -v, 0.f); } nefc++; }
+    }
+    sm[L.limrow + 2 * li] = __int_as_float(r0); sm[L.limrow + 2 * li + 1] = __int_as_float(r1);
+  }
+  // ---- contacts: base Jacobian rows, then the pyramid rows
+  const int nb = D.maxbase;
+  auto bx = sm + L.basev;
+  // #pragma unroll 1
+  for (int c = 0; c < ncon; c++) {
+    auto cr = sm + L.con + 12 * c;
+    const int pr = __float_as_int(cr[7]), dim = __float_as_int(cr[9]);
+    auto pp = D.pair_prm + 16 * pr;
+    const float inc = pp[0] - pp[1];
+    const int rows = cr[0] < inc ? (dim == 1 ? 1 : 2 * (dim - 1)) : 0;
+    const int adr = (rows > 0 && nefc + rows <= njmax) ? nefc : -1;
+    cr[8] = __int_as_float(adr);
+    nefc += rows;
+    const int c1 = D.pair_cg1[pr], c2 = D.pair_cg2[pr];
+    const int f1 = D.cg_frame[c1], f2 = D.cg_frame[c2];
+    const f3 pos = ld3(cr + 1), n = ld3(cr + 4);
+    f3 y, z; makeFrame(n, &y, &z);
+    const int m1a = D.fr_mask[2 * f1], m1b = D.fr_mask[2 * f1 + 1], m2a = D.fr_mask[2 * f2], m2b = D.fr_mask[2 * f2 + 1];
+    auto J = sm + L.conJ + (c * nb) * nv;
+    float vn = 0.f, vy = 0.f, vz = 0.f, vr = 0.f;
+    // #pragma unroll 1
+    for (int k = 0; k < nv; k++) {
+      const int in1 = ((k < 32 ? m1a : m1b) >> (k & 31)) & 1, in2 = ((k < 32 ? m2a : m2b) >> (k & 31)) & 1;
+      f3 jp = mk3(0.f, 0.f, 0.f), jr = jp;
+      if (in1 != in2) {
+        const float s = (float)(in2 - in1);
+        auto cd = sm + L.cdof + 6 * k;
+        jr = ld3(cd) * s;
+        jp = (ld3(cd + 3) + cross(ld3(cd), pos - ld3(sm + L.rootcom + 3 * D.fr_root[D.dof_frame[k]]))) * s;
+      }
+      const float qv = qvel[k];
+      const float jn = dot(n, jp);
+      J[k] = jn; vn = fmaf(jn, qv, vn);
+      if (nb > 1) { const float jy = dot(y, jp), jz = dot(z, jp); J[nv + k] = jy; J[2 * nv + k] = jz; vy = fmaf(jy, qv, vy); vz = fmaf(jz, qv, vz); }
+      if (nb > 3) { const float jt = dot(n, jr); J[3 * nv + k] = jt; vr = fmaf(jt, qv, vr); }
+    }
+    const int bn = c * nb;
+    bx[bn] = vn; if (nb > 1) { bx[bn + 1] = vy; bx[bn + 2] = vz; } if (nb > 3) bx[bn + 3] = vr;
+    if (adr < 0) continue;
+    const float margin = inc, dist = cr[0];
+    const float tran = D.cg_invweight[2 * c1] + D.cg_invweight[2 * c2];
+    const float kb[7] = {pp[14], pp[15], pp[9], pp[10], pp[11], pp[12], pp[13]};
+    if (dim == 1) setRow(slot, sm, adr, ROW_CON, bn, 0.f, -1, dist, margin, tran, kb, bx[bn], 0.f);
+    else {
+      const float mu0 = pp[2] * rsqrtf(D.impratio);
+      const float dA0 = tran + pp[2] * pp[2] * tran;   // first pyramid row sets the shared regulariser
+      // #pragma unroll 1
+      for (int k = 1; k < dim; k++) {
+        const float mu = pp[1 + k];
+        const int bt = bn + k;
+        setRow(slot, sm, adr + 2 * (k - 1), ROW_CON, bn, mu, bt, dist, margin, dA0, kb, bx[bn] + mu * bx[bt], 2.f * mu0 * mu0);
+        setRow(slot, sm, adr + 2 * (k - 1) + 1, ROW_CON, bn, -mu, bt, dist, margin, dA0, kb, bx[bn] - mu * bx[bt], 2.f * mu0 * mu0);
+      }
+    }
+  }
+  if (nefc > njmax) { *status |= MYO_WORLD_NEFC_OVERFLOW; nefc = njmax; }
+  return nefc;
+}
+
+// ------------------------------------------------------------------------------------------ Newton solver (mj_fwdConstraint)
+__device__ __noinline__ void mulMsparse(int slot, SP qM, SP x, SP out) {
+  const DevModel& D = tP[slot].D;
+  const int nv = D.nv;
+  // #pragma unroll 1
+  for (int i = 0; i < nv; i++) out[i] = 0.f;
+  // #pragma unroll 1
+  for (int i = 0; i < nv; i++) {
+    const int a = D.dof_Madr[i], d = D.dof_rowlen[i];
+    const float xi = x[i];
+    float acc = qM[a] * xi;
+    // #pragma unroll 1
+    for (int s = 1; s < d; s++) { const int j = D.M_col[a + s]; const float m = qM[a + s]; acc = fmaf(m, x[j], acc); out[j] = fmaf(m, xi, out[j]); }
+    out[i] += acc;
+  }
+}
+__device__ __forceinline__ bool rowOn(int d0, float jar) { return ((d0 & 3) == ROW_EQ) || jar < 0.f; }
+// jar = J x - aref for all rows, returns the constraint cost; force/active are implied by jar
+__device__ __noinline__ float residualCost(int slot, SP sm, int ncon, int nefc, SP x) {
+  const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
+  auto bx = sm + L.basev;
+  baseMul(slot, sm, ncon, x, bx);
+  float cost = 0.f;
+  // #pragma unroll 1
+  for (int r = 0; r < nefc; r++) {
+    const float jar = rowMul(slot, sm, r, x, bx) - EFC(E_AREF, r);
+    EFC(E_JAR, r) = jar;
+    if (rowOn(EFCI(E_DESC0, r), jar)) cost = fmaf(0.5f * EFC(E_D, r) * jar, jar, cost);
+  }
+  return cost;
+}
+// forces from jar, then out = J^T f
+__device__ __noinline__ void constraintForce(int slot, SP sm, int ncon, int nefc, SP out) {
+  const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
+  const int nv = D.nv, nb = D.maxbase;
+  // #pragma unroll 1
+  for (int k = 0; k < nv; k++) out[k] = 0.f;
+  // #pragma unroll 1
+  for (int r = 0; r < nefc; r++) {
+    const int d0 = EFCI(E_DESC0, r), type = d0 & 3, id = d0 >> 2;
+    const float jar = EFC(E_JAR, r);
+    const float f = rowOn(d0, jar) ? -EFC(E_D, r) * jar : 0.f;
+    EFC(E_FORCE, r) = f;
+    if (f == 0.f || type == ROW_CON) continue;
+    const float coef = EFC(E_COEF, r);
+    if (type == ROW_LIMJ) out[D.limj_dof[id]] += coef * f;
+    else if (type == ROW_EQ) { out[D.eq_dof1[id]] += f; const int d2 = D.eq_dof2[id]; if (d2 >= 0) out[d2] += coef * f; }
+    else {
+      const int t = D.limt_ten[id];
+      // #pragma unroll 1
+      for (int n = D.ten_nzstart[t]; n < D.ten_nzstart[t + 1]; n++) out[D.nz_dof[n]] += coef * f * sm[L.tenJ + n];
+    }
+  }
+  // #pragma unroll 1
+  for (int c = 0; c < ncon; c++) {
+    auto cr = sm + L.con + 12 * c;
+    const int adr = __float_as_int(cr[8]), dim = __float_as_int(cr[9]);
+    if (adr < 0) continue;
+    float bf[4] = {0.f, 0.f, 0.f, 0.f};
+    if (dim == 1) bf[0] = EFC(E_FORCE, adr);
+    else
+      // #pragma unroll 1
+      for (int k = 1; k < dim; k++) {
+        const float fp = EFC(E_FORCE, adr + 2 * (k - 1)), fm = EFC(E_FORCE, adr + 2 * (k - 1) + 1);
+        bf[0] += fp + fm; bf[k] = EFC(E_COEF, adr + 2 * (k - 1)) * (fp - fm);
+      }
+    if (bf[0] == 0.f && bf[1] == 0.f && bf[2] == 0.f && bf[3] == 0.f) continue;
+    auto J = sm + L.conJ + (c * nb) * nv;
+    // #pragma unroll 1
+    for (int k = 0; k < nv; k++) {
+      float acc = fmaf(J[k], bf[0], out[k]);
+      if (dim > 1) { acc = fmaf(J[nv + k], bf[1], acc); acc = fmaf(J[2 * nv + k], bf[2], acc); }
+      if (dim > 3) acc = fmaf(J[3 * nv + k], bf[3], acc);
+      out[k] = acc;
+    }
+  }
+}
+// H = M + J^T D_active J (lower triangle), Cholesky in place
+__device__ __noinline__ void hessianFactor(int slot, SP sm, int ncon, int nefc) {
+  const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
+  const int nv = D.nv, nb = D.maxbase;
+  auto H = sm + L.H;
+  // #pragma unroll 1
+  for (int i = 0; i < nv * nv; i++) H[i] = 0.f;
+  // #pragma unroll 1
+  for (int e = 0; e < D.nM; e++) H[D.M_row[e] * nv + D.M_col[e]] = sm[L.qM + e];
+  // #pragma unroll 1
+  for (int r = 0; r < nefc; r++) {
+    const int d0 = EFCI(E_DESC0, r), type = d0 & 3, id = d0 >> 2;
+    if (type == ROW_CON || !rowOn(d0, EFC(E_JAR, r))) continue;
+    const float Dr = EFC(E_D, r), coef = EFC(E_COEF, r);
+    if (type == ROW_LIMJ) { const int k = D.limj_dof[id]; H[k * nv + k] += Dr; }
+    else if (type == ROW_EQ) {
+      const int d1 = D.eq_dof1[id], d2 = D.eq_dof2[id];
+      H[d1 * nv + d1] += Dr;
+      if (d2 >= 0) { H[max(d1, d2) * nv + min(d1, d2)] += Dr * coef; H[d2 * nv + d2] += Dr * coef * coef; }
+    } else {
+      const int t = D.limt_ten[id], n0 = D.ten_nzstart[t], n1 = D.ten_nzstart[t + 1];
+      // #pragma unroll 1
+      for (int a = n0; a < n1; a++)
+        // #pragma unroll 1
+        for (int b = n0; b <= a; b++) H[D.nz_dof[a] * nv + D.nz_dof[b]] += Dr * sm[L.tenJ + a] * sm[L.tenJ + b];   // nz sorted by dof
+    }
+  }
+  // #pragma unroll 1
+  for (int c = 0; c < ncon; c++) {
+    auto cr = sm + L.con + 12 * c;
+    const int adr = __float_as_int(cr[8]), dim = __float_as_int(cr[9]);
+    if (adr < 0) continue;
+    // weights in base-row space: W = sum_p D_p w_p w_p^T, w_p = e_n +- mu e_t
+    float Wnn = 0.f, Wnt[3] = {0.f, 0.f, 0.f}, Wtt[3] = {0.f, 0.f, 0.f};
+    if (dim == 1) { if (rowOn(EFCI(E_DESC0, adr), EFC(E_JAR, adr))) Wnn = EFC(E_D, adr); }
+    else
+      // #pragma unroll 1
+      for (int k = 1; k < dim; k++) {
+        const int r0 = adr + 2 * (k - 1);
+        const float mu = EFC(E_COEF, r0);
+        const float Dp = EFC(E_JAR, r0) < 0.f ? EFC(E_D, r0) : 0.f, Dm = EFC(E_JAR, r0 + 1) < 0.f ? EFC(E_D, r0 + 1) : 0.f;
+        Wnn += Dp + Dm; Wnt[k - 1] = mu * (Dp - Dm); Wtt[k - 1] = mu * mu * (Dp + Dm);
+      }
+    if (Wnn == 0.f) continue;
+    auto Jn = sm + L.conJ + (c * nb) * nv;
+    // #pragma unroll 1
+    for (int r = 0; r < nv; r++) {
+      // u_r = W-weighted combination for row r:  H[r, c] += sum_k u_k[r] * J_k[c]
+      const float jn = Jn[r];
+      float un = Wnn * jn, ut[3] = {0.f, 0.f, 0.f};
+      bool any = jn != 0.f;
+      // #pragma unroll 1
+      for (int k = 1; k < dim; k++) {
+        const float jt = Jn[k * nv + r];
+        un = fmaf(Wnt[k - 1], jt, un); ut[k - 1] = fmaf(Wnt[k - 1], jn, Wtt[k - 1] * jt);
+        any |= jt != 0.f;
+      }
+      if (!any) continue;
+      // #pragma unroll 1
+      for (int cc = 0; cc <= r; cc++) {
+        float acc = fmaf(un, Jn[cc], H[r * nv + cc]);
+        for (int k = 1; k < dim; k++) acc = fmaf(ut[k - 1], Jn[k * nv + cc], acc);
+        H[r * nv + cc] = acc;
+      }
+    }
+  }
+  // Cholesky (row-oriented, lower triangle in place)
+  // #pragma unroll 1
+  for (int j = 0; j < nv; j++) {
+    auto Hj = H + j * nv;
+    // #pragma unroll 1
+    for (int k = 0; k < j; k++) {
+      auto Hk = H + k * nv;
+      float s = Hj[k];
+      // #pragma unroll 1
+      for (int q = 0; q < k; q++) s = fmaf(-Hj[q], Hk[q], s);
+      Hj[k] = s / Hk[k];
+    }
+    float s = Hj[j];
+    // #pragma unroll 1
+    for (int q = 0; q < j; q++) s = fmaf(-Hj[q], Hj[q], s);
+    Hj[j] = sqrtf(fmaxf(s, MINVAL));
+  }
+}
+__device__ __noinline__ void cholSolve(int slot, SP H, SP x) {
+  const int nv = tP[slot].D.nv;
+  // #pragma unroll 1
+  for (int j = 0; j < nv; j++) {
+    float s = x[j];
+    // #pragma unroll 1
+    for (int k = 0; k < j; k++) s = fmaf(-H[j * nv + k], x[k], s);
+    x[j] = s / H[j * nv + j];
+  }
+  // #pragma unroll 1
+  for (int j = nv - 1; j >= 0; j--) {
+    const float xj = x[j] / H[j * nv + j];
+    x[j] = xj;
+    // #pragma unroll 1
+    for (int r = 0; r < j; r++) x[r] = fmaf(-H[j * nv + r], xj, x[r]);
+  }
+}
+struct LsPt { float alpha, cost, d0, d1; };
+__device__ __noinline__ LsPt lsEval(int slot, SP sm, int nefc, float a, const float* qg) {
+  const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
+  float q0 = qg[0], q1 = qg[1], q2 = qg[2];
+  // #pragma unroll 1
+  for (int r = 0; r < nefc; r++) {
+    const float jar = EFC(E_JAR, r), jv = EFC(E_JV, r), x = fmaf(a, jv, jar);
+    if (rowOn(EFCI(E_DESC0, r), x)) {
+      const float Dr = EFC(E_D, r);
+      q0 = fmaf(0.5f * Dr * jar, jar, q0); q1 = fmaf(Dr * jar, jv, q1); q2 = fmaf(0.5f * Dr * jv, jv, q2);
+    }
+  }
+  LsPt p; p.alpha = a; p.cost = a * a * q2 + a * q1 + q0; p.d0 = 2.f * a * q2 + q1; p.d1 = 2.f * q2;
+  if (p.d1 <= 0.f) p.d1 = MINVAL;
+  return p;
+}
+__device__ __noinline__ int solveNewton(int slot, SP sm, int ncon, int nefc, int* status) {
+  const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
+  const int nv = D.nv;
+  auto qacc = sm + L.qacc; auto Ma = sm + L.nvec; auto grad = Ma + nv; auto search = grad + nv; auto Mv = search + nv;
+  auto tmp = Mv + nv;
+  auto smooth = sm + L.smooth; auto qas = sm + L.qacc_smooth;
+  const float scale = 1.f / (D.meaninertia * (float)max(1, nv));
+  // warm start: cheaper of qacc_warmstart and qacc_smooth
+  float costW = 3.4e38f;
+  if (!(D.disableflags & DSBL_WARMSTART)) {
+    mulMsparse(slot, sm + L.qM, sm + L.warm, Ma);
+    float g = 0.f;
+    // #pragma unroll 1
+    for (int k = 0; k < nv; k++) g = fmaf(0.5f * (Ma[k] - smooth[k]), sm[L.warm + k] - qas[k], g);
+    costW = g + residualCost(slot, sm, ncon, nefc, sm + L.warm);
+  }
+  const float costS = residualCost(slot, sm, ncon, nefc, qas);
+  const bool useWarm = !(costW > costS);
+  // #pragma unroll 1
+  for (int k = 0; k < nv; k++) qacc[k] = useWarm ? sm[L.warm + k] : qas[k];
+  mulMsparse(slot, sm + L.qM, qacc, Ma);
+  float gauss = 0.f;
+  // #pragma unroll 1
+  for (int k = 0; k < nv; k++) gauss = fmaf(0.5f * (Ma[k] - smooth[k]), qacc[k] - qas[k], gauss);
+  float cost = gauss + residualCost(slot, sm, ncon, nefc, qacc);
+  int iter = 0;
+  // #pragma unroll 1
+  for (;;) {
+    // gradient and termination tests
+    constraintForce(slot, sm, ncon, nefc, tmp);
+    float gn = 0.f;
+    // #pragma unroll 1
+    for (int k = 0; k < nv; k++) { const float g = Ma[k] - smooth[k] - tmp[k]; grad[k] = g; search[k] = g; gn = fmaf(g, g, gn); }
+    gn = sqrtf(gn);
+    if (iter > 0 && scale * gn < D.tolerance) break;
+    if (iter >= D.iterations) { *status |= MYO_WORLD_SOLVER_MAXITER; break; }
+    hessianFactor(slot, sm, ncon, nefc);
+    cholSolve(slot, sm + L.H, search);
+    float sn = 0.f;
+    // #pragma unroll 1
+    for (int k = 0; k < nv; k++) { const float s = -search[k]; search[k] = s; sn = fmaf(s, s, sn); }
+    sn = sqrtf(sn);
+    if (sn < MINVAL) break;
+    // exact line search along `search`
+    mulMsparse(slot, sm + L.qM, search, Mv);
+    auto bx = sm + L.basev;
+    baseMul(slot, sm, ncon, search, bx);
+    // #pragma unroll 1
+    for (int r = 0; r < nefc; r++) EFC(E_JV, r) = rowMul(slot, sm, r, search, bx);
+    float g1 = 0.f, g2 = 0.f;
+    // #pragma unroll 1
+    for (int k = 0; k < nv; k++) { g1 = fmaf(search[k], Ma[k] - smooth[k], g1); g2 = fmaf(0.5f * search[k], Mv[k], g2); }
+    const float qg[3] = {gauss, g1, g2};
+    const float gtol = D.tolerance * D.ls_tolerance * sn / scale;
+    int lsiter = 0;
+    LsPt p0 = lsEval(slot, sm, nefc, 0.f, qg); lsiter++;
+    LsPt p1 = lsEval(slot, sm, nefc, p0.alpha - p0.d0 / p0.d1, qg); lsiter++;
+    if (p0.cost < p1.cost) p1 = p0;
+    bool done = fabsf(p1.d0) < gtol;
+    if (!done) {
+      const float dir = p1.d0 < 0.f ? 1.f : -1.f;
+      LsPt p2 = p1; bool have2 = false;
+      // #pragma unroll 1
+      while (p1.d0 * dir <= -gtol && lsiter < D.ls_iterations) {
+        p2 = p1; have2 = true;
+        p1 = lsEval(slot, sm, nefc, p1.alpha - p1.d0 / p1.d1, qg); lsiter++;
+        if (fabsf(p1.d0) < gtol) { done = true; break; }
+      }
+      if (!done && lsiter < D.ls_iterations && have2) {
+        LsPt lo = p2, hi = p1;
+        // #pragma unroll 1
+        while (lsiter < D.ls_iterations) {
+          bool moved = false;
+          LsPt best = lo.cost < hi.cost ? lo : hi;
+          const float ca[3] = {lo.alpha - lo.d0 / lo.d1, hi.alpha - hi.d0 / hi.d1, 0.5f * (lo.alpha + hi.alpha)};
+          LsPt cand[3];
+          // #pragma unroll 1
+          for (int q = 0; q < 3; q++) { cand[q] = lsEval(slot, sm, nefc, ca[q], qg); lsiter++; }
+          // #pragma unroll 1
+          for (int q = 0; q < 3; q++) {
+            if (done) break;
+            const LsPt c = cand[q];
+            if (fabsf(c.d0) < gtol) { p1 = c; done = true; break; }
+            if (!((c.alpha - lo.alpha) * dir > 0.f && (hi.alpha - c.alpha) * dir > 0.f)) continue;
+            if (c.d0 * dir < 0.f) lo = c; else hi = c;
+            moved = true;
+            if (c.cost < best.cost) best = c;
+          }
+          if (done) break;
+          if (!moved) { p1 = best; break; }
+          p1 = lo.cost < hi.cost ? lo : hi;
+        }
+      }
+    }
+    const float alpha = p1.alpha;
+    if (alpha == 0.f) break;
+    // #pragma unroll 1
+    for (int k = 0; k < nv; k++) { qacc[k] = fmaf(alpha, search[k], qacc[k]); Ma[k] = fmaf(alpha, Mv[k], Ma[k]); }
+    float c2 = 0.f;
+    // #pragma unroll 1
+    for (int r = 0; r < nefc; r++) {
+      const float jar = fmaf(alpha, EFC(E_JV, r), EFC(E_JAR, r));
+      EFC(E_JAR, r) = jar;
+      if (rowOn(EFCI(E_DESC0, r), jar)) c2 = fmaf(0.5f * EFC(E_D, r) * jar, jar, c2);
+    }
+    float g = 0.f;
+    // #pragma unroll 1
+    for (int k = 0; k < nv; k++) g = fmaf(0.5f * (Ma[k] - smooth[k]), qacc[k] - qas[k], g);
+    gauss = g;
+    const float newcost = gauss + c2;
+    iter++;
+    const float improvement = scale * (cost - newcost);
+    cost = newcost;
+    if (improvement < D.tolerance) break;
+  }
+  constraintForce(slot, sm, ncon, nefc, sm + L.qfrc_con);
+  return iter;
+}
+
+// ------------------------------------------------------------------------------------------ contact / efc outputs
+__device__ __noinline__ void writeConstraintOutputs(int slot, int fslot, SP sm, World W, int ncon, int nefc, int niter) {
+  const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L; const FieldPtrs& F = tP[fslot].F;
+  const int nv = D.nv, ncm = D.nconmax, njm = D.njmax;
+  void* p;
+  if ((p = F.p[MYO_F_NCON])) OUTI(p, 0) = ncon;
+  if ((p = F.p[MYO_F_NEFC])) OUTI(p, 0) = nefc;
+  if ((p = F.p[MYO_F_SOLVER_NITER])) OUTI(p, 0) = niter;
+  void* cg = F.p[MYO_F_CONTACT_GEOM]; void* cdim = F.p[MYO_F_CONTACT_DIM]; void* cadr = F.p[MYO_F_CONTACT_EFC_ADDRESS];
+  void* cdist = F.p[MYO_F_CONTACT_DIST]; void* cpos = F.p[MYO_F_CONTACT_POS]; void* cfr = F.p[MYO_F_CONTACT_FRAME];
+  void* cinc = F.p[MYO_F_CONTACT_INCLUDEMARGIN]; void* cfri = F.p[MYO_F_CONTACT_FRICTION]; void* csr = F.p[MYO_F_CONTACT_SOLREF];
+  void* csi = F.p[MYO_F_CONTACT_SOLIMP];
+  if (cg || cdim || cadr || cdist || cpos || cfr || cinc || cfri || csr || csi) {
+    // #pragma unroll 1
+    for (int c = 0; c < ncm; c++) {
+      const bool on = c < ncon;
+      auto cr = sm + L.con + 12 * c;
+      const int pr = on ? __float_as_int(cr[7]) : 0;
+      auto pp = D.pair_prm + 16 * pr;
+      if (cg) { OUTI(cg, 2 * c) = on ? D.cg_geom[D.pair_cg1[pr]] : -1; OUTI(cg, 2 * c + 1) = on ? D.cg_geom[D.pair_cg2[pr]] : -1; }
+      if (cdim) OUTI(cdim, c) = on ? __float_as_int(cr[9]) : 0;
+      if (cadr) OUTI(cadr, c) = on ? __float_as_int(cr[8]) : -1;
+      if (cdist) OUTF(cdist, c) = on ? cr[0] : 0.f;
+      if (cpos) for (int k = 0; k < 3; k++) OUTF(cpos, 3 * c + k) = on ? cr[1 + k] : 0.f;
+      if (cfr) {
+        f3 n = mk3(0.f, 0.f, 0.f), y = n, z = n;
+        if (on) { n = ld3(cr + 4); makeFrame(n, &y, &z); }
+        OUTF(cfr, 9 * c) = n.x; OUTF(cfr, 9 * c + 1) = n.y; OUTF(cfr, 9 * c + 2) = n.z; OUTF(cfr, 9 * c + 3) = y.x; OUTF(cfr, 9 * c + 4) = y.y;
+        OUTF(cfr, 9 * c + 5) = y.z; OUTF(cfr, 9 * c + 6) = z.x; OUTF(cfr, 9 * c + 7) = z.y; OUTF(cfr, 9 * c + 8) = z.z;
+      }
+      if (cinc) OUTF(cinc, c) = on ? pp[0] - pp[1] : 0.f;
+      if (cfri) for (int k = 0; k < 5; k++) OUTF(cfri, 5 * c + k) = on ? pp[2 + k] : 0.f;
+      if (csr) for (int k = 0; k < 2; k++) OUTF(csr, 2 * c + k) = on ? pp[7 + k] : 0.f;
+      if (csi) for (int k = 0; k < 5; k++) OUTF(csi, 5 * c + k) = on ? pp[9 + k] : 0.f;
+    }
+  }
+  void* epos = F.p[MYO_F_EFC_POS]; void* emar = F.p[MYO_F_EFC_MARGIN]; void* eD = F.p[MYO_F_EFC_D]; void* earef = F.p[MYO_F_EFC_AREF];
+  void* efrc = F.p[MYO_F_EFC_FORCE]; void* etyp = F.p[MYO_F_EFC_TYPE]; void* eJ = F.p[MYO_F_EFC_J];
+  if (epos || emar || eD || earef || efrc || etyp || eJ) {
+    // #pragma unroll 1
+    for (int r = 0; r < njm; r++) {
+      const bool on = r < nefc;
+      if (epos) OUTF(epos, r) = on ? EFC(E_POS, r) : 0.f;
+      if (emar) OUTF(emar, r) = on ? EFC(E_MARGIN, r) : 0.f;
+      if (eD) OUTF(eD, r) = on ? EFC(E_D, r) : 0.f;
+      if (earef) OUTF(earef, r) = on ? EFC(E_AREF, r) : 0.f;
+      if (efrc) OUTF(efrc, r) = on ? EFC(E_FORCE, r) : 0.f;
+      const int d0 = on ? EFCI(E_DESC0, r) : 0, type = d0 & 3, id = d0 >> 2;
+      if (etyp) OUTI(etyp, r) = !on ? -1 : (type == ROW_EQ ? 0 : (type == ROW_LIMJ ? 3 : (type == ROW_LIMT ? 4 : (EFCI(E_DESC1, r) < 0 ? 5 : 6))));
+      if (eJ) {
+        const float coef = on ? EFC(E_COEF, r) : 0.f;
+        const int t1 = on && type == ROW_CON ? EFCI(E_DESC1, r) : -1;
+        // #pragma unroll 1
+        for (int k = 0; k < nv; k++) {
+          float v = 0.f;
+          if (on) {
+            if (type == ROW_LIMJ) v = D.limj_dof[id] == k ? coef : 0.f;
+            else if (type == ROW_EQ) v = D.eq_dof1[id] == k ? 1.f : (D.eq_dof2[id] == k ? coef : 0.f);
+            else if (type == ROW_CON) v = sm[L.conJ + id * nv + k] + (t1 >= 0 ? coef * sm[L.conJ + t1 * nv + k] : 0.f);
+            else { const int t = D.limt_ten[id]; for (int q = D.ten_nzstart[t]; q < D.ten_nzstart[t + 1]; q++) if (D.nz_dof[q] == k) v = coef * sm[L.tenJ + q]; }
+          }
+          OUTF(eJ, r * nv + k) = v;
+        }
+      }
+    }
+  }
+}
+
+__device__ __forceinline__ bool anyBad(SP v, int n) {
+  bool bad = false;
+  // #pragma unroll 1
+  for (int i = 0; i < n; i++) bad |= !(fabsf(v[i]) < 1e10f);
+  return bad;
+}
+__device__ __noinline__ void resetState(int slot, SP sm) {
+  const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
+  for (int i = 0; i < D.nq; i++) sm[L.qpos + i] = D.qpos0[i];
+  for (int i = 0; i < D.nv; i++) { sm[L.qvel + i] = 0.f; sm[L.warm + i] = 0.f; }
+  for (int i = 0; i < D.na; i++) sm[L.act + i] = 0.f;
+}
+
+// mj_forward for one world: everything from the state in `sm`; returns nefc
+__device__ __forceinline__ void forwardWorld(int slot, int fslot, SP sm, World W, bool last, int* status, int* ncon_o, int* nefc_o, int* niter_o) {
+  const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
+  const int nv = D.nv;
+  kinematics(slot, sm);
+  comPos(slot, sm);
+  if (last) writePositionOutputs(slot, fslot, sm, W);
+  tendons(slot, fslot, sm, W);
+  inertia(slot, fslot, sm, W);
+  const int ncon = (D.disableflags & (DSBL_CONTACT | DSBL_CONSTRAINT)) ? 0 : collision(slot, sm, status);
+  velocity(slot, fslot, sm, W);
+  actuation(slot, fslot, sm, W);
+  const int nefc = makeConstraint(slot, sm, ncon, status);
+  int niter = 0;
+  if (nefc == 0) {
+    for (int i = 0; i < nv; i++) { const float a = sm[L.qacc_smooth + i]; sm[L.qacc + i] = a; sm[L.warm + i] = a; sm[L.qfrc_con + i] = 0.f; }
+  } else {
+    niter = solveNewton(slot, sm, ncon, nefc, status);
+    for (int i = 0; i < nv; i++) sm[L.warm + i] = sm[L.qacc + i];
+  }
+  *ncon_o = ncon; *nefc_o = nefc; *niter_o = niter;
+}
+
+// One warp = SCR_STRIDE worlds, TEAM lanes each.  `scratch`: [nwarps][SmemLayout.total][SCR_STRIDE] floats.
+__global__ void __launch_bounds__(32) stepKernel(int slot, int nworld, int nsub, int forward_only, const int* __restrict__ mask, int do_reset,
+                                                 float* __restrict__ scratch) {
+  const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L; const FieldPtrs& F = tP[slot].F;
+  const int lane = threadIdx.x & 31, g = lane / TEAM;
+  World W; W.w = (size_t)blockIdx.x * SCR_STRIDE + g; W.nw = (size_t)nworld;
+  if (W.w >= W.nw) return;
+  SP sm; sm.p = scratch + (size_t)blockIdx.x * L.total * SCR_STRIDE + g;
+  if (do_reset && mask && !mask[W.w]) return;
+  const int nq = D.nq, nv = D.nv, na = D.na, nu = D.nu;
+  void* gq = F.p[MYO_F_QPOS]; void* gv = F.p[MYO_F_QVEL]; void* ga = F.p[MYO_F_ACT]; void* gc = F.p[MYO_F_CTRL];
+  void* gw = F.p[MYO_F_QACC_WARMSTART]; void* gt = F.p[MYO_F_TIME]; void* gs = F.p[MYO_F_STATUS];
+  int status = gs ? OUTI(gs, 0) : 0;
+  float time = OUTF(gt, 0);
+  if (do_reset) {
+    resetState(slot, sm);
+    for (int i = 0; i < nu; i++) sm[L.ctrl + i] = 0.f;
+    time = 0.f; status = 0;
+  } else {
+    for (int i = 0; i < nq; i++) sm[L.qpos + i] = OUTF(gq, i);
+    for (int i = 0; i < nv; i++) { sm[L.qvel + i] = OUTF(gv, i); sm[L.warm + i] = OUTF(gw, i); }
+    for (int i = 0; i < na; i++) sm[L.act + i] = OUTF(ga, i);
+    for (int i = 0; i < nu; i++) sm[L.ctrl + i] = OUTF(gc, i);
+  }
+  const int nloop = forward_only ? 1 : nsub;
+  // #pragma unroll 1
+  for (int sub = 0; sub < nloop; sub++) {
+    const bool last = sub == nloop - 1;
+    const int fslot = last ? slot : MYO_NSLOT;
+    if (!forward_only) {   // mj_checkPos / mj_checkVel
+      if (anyBad(sm + L.qpos, nq)) { resetState(slot, sm); status |= MYO_WORLD_BADQPOS; }
+      if (anyBad(sm + L.qvel, nv)) { resetState(slot, sm); status |= MYO_WORLD_BADQVEL; }
+    }
+    int ncon = 0, nefc = 0, niter = 0;
+    forwardWorld(slot, fslot, sm, W, last, &status, &ncon, &nefc, &niter);
+    if (!forward_only && anyBad(sm + L.qacc, nv)) {   // mj_checkAcc: reset the world and redo its forward pass
+      resetState(slot, sm);
+      status |= MYO_WORLD_BADQACC;
+      forwardWorld(slot, fslot, sm, W, last, &status, &ncon, &nefc, &niter);
+    }
+    if (last) {
+      writeConstraintOutputs(slot, fslot, sm, W, ncon, nefc, niter);
+      void* o;
+      if ((o = F.p[MYO_F_QACC])) for (int i = 0; i < nv; i++) OUTF(o, i) = sm[L.qacc + i];
+      if ((o = F.p[MYO_F_QFRC_CONSTRAINT])) for (int i = 0; i < nv; i++) OUTF(o, i) = sm[L.qfrc_con + i];
+      if ((o = F.p[MYO_F_QFRC_INVERSE])) for (int i = 0; i < nv; i++) OUTF(o, i) = 0.f;
+    }
+    if (forward_only) break;
+    // ---- mj_Euler with implicit joint damping
+    const float h = D.timestep;
+    auto qa = sm + L.tmpv;
+    if (D.any_damping) {
+      // #pragma unroll 1
+      for (int i = 0; i < nv; i++) {
+        const int a = D.dof_Madr[i], d = D.dof_rowlen[i];
+        sm[L.qH + a] = sm[L.qM + a] + h * D.dof_damping[i];
+        for (int s = 1; s < d; s++) sm[L.qH + a + s] = sm[L.qM + a + s];
+        qa[i] = sm[L.smooth + i] + sm[L.qfrc_con + i];
+      }
+      factorLDL(slot, sm + L.qH, sm + L.qHinv);
+      solveLDL(slot, sm + L.qH, sm + L.qHinv, qa);
+    } else {
+      for (int i = 0; i < nv; i++) qa[i] = sm[L.qacc + i];
+    }
+    if (!(D.disableflags & DSBL_ACTUATION))
+      // #pragma unroll 1
+      for (int i = 0; i < nu; i++) {
+        const int aa = D.act_actadr[i];
+        if (aa < 0) continue;
+        float a = fmaf(h, sm[L.actdot + aa], sm[L.act + aa]);
+        if (D.act_flags[i] & ACT_ACTLIMITED) a = clipf(a, D.act_actrange[2 * i], D.act_actrange[2 * i + 1]);
+        sm[L.act + aa] = a;
+      }
+    for (int i = 0; i < nv; i++) sm[L.qvel + i] = fmaf(h, qa[i], sm[L.qvel + i]);
+    // #pragma unroll 1
+    for (int j = 0; j < D.njnt; j++) {
+      const int qa_ = D.jnt_qposadr[j], da = D.jnt_dofadr[j];
+      if (D.jnt_type[j] == JNT_FREE) {
+        for (int k = 0; k < 3; k++) sm[L.qpos + qa_ + k] = fmaf(h, sm[L.qvel + da + k], sm[L.qpos + qa_ + k]);
+        const f3 wv = ld3(sm + L.qvel + da + 3);
+        const float ang = norm3(wv) * h;
+        if (ang > 0.f) {
+          const f3 ax = unit3(wv);
+          float sn, cs; sincos_(0.5f * ang, &sn, &cs);
+          f4 dq; dq.w = cs; dq.x = ax.x * sn; dq.y = ax.y * sn; dq.z = ax.z * sn;
+          st4(sm + L.qpos + qa_ + 3, qnormalize(qmul(ld4(sm + L.qpos + qa_ + 3), dq)));
+        }
+      } else sm[L.qpos + qa_] = fmaf(h, sm[L.qvel + da], sm[L.qpos + qa_]);
+    }
+    time += h;
+  }
+  // ---- state out
+  if (!forward_only || do_reset) {
+    for (int i = 0; i < nq; i++) OUTF(gq, i) = sm[L.qpos + i];
+    for (int i = 0; i < nv; i++) OUTF(gv, i) = sm[L.qvel + i];
+    for (int i = 0; i < na; i++) OUTF(ga, i) = sm[L.act + i];
+    OUTF(gt, 0) = time;
+  }
+  for (int i = 0; i < nv; i++) OUTF(gw, i) = sm[L.warm + i];
+  if (gs) OUTI(gs, 0) = status;
+}
+
+// known-answer hook for the rotation helpers above (tests/: reference KATs of myosuite/utils/quat_math.py)
+__global__ void quatKatKernel(int n, const float* __restrict__ qa, const float* __restrict__ qb, float* __restrict__ prod,
+                              float* __restrict__ mat, float* __restrict__ rotated) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const f4 a = ld4(qa + 4 * i), b = ld4(qb + 4 * i);
+  st4(prod + 4 * i, qmul(a, b));
+  float R[9]; q2m(R, qnormalize(a));
+  for (int k = 0; k < 9; k++) mat[9 * i + k] = R[k];
+  st3(rotated + 3 * i, mulM(R, mk3(b.x, b.y, b.z)));
+}
+
+int64_t g_tpw_launches = 0;
+
+}  // namespace
+
+int64_t myo_tpw_launch_counter() { return g_tpw_launches; }
+int myo_tpw_param_slots() { return MYO_NSLOT; }
+
+int myo_tpw_upload_params(int slot, const DevModel& D, const SmemLayout& L, const FieldPtrs& F, void* stream) {
+  static TParams staging[MYO_NSLOT];   // must outlive the async copy
+  if (slot < 0 || slot >= MYO_NSLOT) return -1;
+  TParams& P = staging[slot];
+  P.D = D; P.L = L; P.F = F;
+  return cudaMemcpyToSymbolAsync(tP, &P, sizeof(TParams), (size_t)slot * sizeof(TParams), cudaMemcpyHostToDevice, (cudaStream_t)stream) == cudaSuccess ? 0 : -1;
+}
+
+int myo_tpw_launch_step(int slot, const SmemLayout& L, int nworld, int nsub, int forward_only, const int* reset_mask, int do_reset,
+                        float* scratch, void* stream) {
+  const int nwarp = (nworld + SCR_STRIDE - 1) / SCR_STRIDE;
+  stepKernel<<<nwarp, 32, 0, (cudaStream_t)stream>>>(slot, nworld, nsub, forward_only, reset_mask, do_reset, scratch);
+  g_tpw_launches++;
+  return cudaPeekAtLastError() == cudaSuccess ? 0 : -1;
+}
+// floats of scratch a batch of nworld worlds needs
+size_t myo_tpw_scratch_floats(const SmemLayout& L, int nworld) {
+  return (size_t)((nworld + SCR_STRIDE - 1) / SCR_STRIDE) * L.total * SCR_STRIDE;
+}
+
+int myo_tpw_launch_quat_kat(int n, const float* qa, const float* qb, float* prod, float* mat, float* rotated, void* stream) {
+  quatKatKernel<<<(n + 127) / 128, 128, 0, (cudaStream_t)stream>>>(n, qa, qb, prod, mat, rotated);
+  g_tpw_launches++;
+  return cudaPeekAtLastError() == cudaSuccess ? 0 : -1;
+}
