@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -24,12 +25,26 @@ struct myo_batch {
   FieldPtrs F;
   int nworld;
   int slot;      // constant-memory parameter slot
+  const TeamVariant* kern;   // step kernel variant (lanes per world) chosen for this batch size
   bool dirty;    // parameters changed since the last upload
   float* scratch; // per-world intermediates, [nwarps][L.total][worlds per warp]
   std::vector<void*> owned;
 };
 
 namespace {
+const TeamVariant kVariants[] = {
+    {1, myo_team_upload_1, myo_team_launch_1, myo_team_scratch_1}, {2, myo_team_upload_2, myo_team_launch_2, myo_team_scratch_2},
+    {4, myo_team_upload_4, myo_team_launch_4, myo_team_scratch_4}, {8, myo_team_upload_8, myo_team_launch_8, myo_team_scratch_8},
+    {16, myo_team_upload_16, myo_team_launch_16, myo_team_scratch_16}};
+int64_t g_launches = 0;
+// lanes per world: the step is latency-bound, so small batches get wider teams (more warps per SM)
+const TeamVariant* pickVariant(int nworld) {
+  int team = 1;
+  while (team < 8 && (int64_t)nworld * team < (int64_t)148 * 8 * 32) team <<= 1;
+  if (const char* e = getenv("MYO_TEAM")) team = atoi(e);
+  for (const TeamVariant& v : kVariants) if (v.team == team) return &v;
+  return &kVariants[2];
+}
 thread_local std::string g_err;
 bool g_slot_used[64] = {false};
 int fail(int code, const std::string& msg) { g_err = msg; return code; }
@@ -101,7 +116,7 @@ int checkReady(myo_batch* b) {
 extern "C" {
 
 const char* myo_last_error(void) { return g_err.c_str(); }
-int64_t myo_launch_count(void) { return myo_tpw_launch_counter(); }
+int64_t myo_launch_count(void) { return g_launches; }
 const char* myo_field_name(int field) { return (field >= 0 && field < MYO_F_COUNT) ? kFieldNames[field] : ""; }
 int myo_field_itemsize(int field) { (void)field; return 4; }
 int myo_field_is_int(int field) { return isIntField(field) ? 1 : 0; }
@@ -137,7 +152,7 @@ int myo_batch_create(const myo_model* m, int nworld, int nconmax, int njmax, myo
   if (cudaSetDevice(m->device) != cudaSuccess) return fail(MYO_ERR_CUDA, "cudaSetDevice failed");
   myo_batch* b = new myo_batch();
   b->model = m; b->D = m->D; b->nworld = nworld; b->slot = -1; b->dirty = true;
-  for (int i = 0; i < myo_tpw_param_slots(); i++) if (!g_slot_used[i]) { b->slot = i; g_slot_used[i] = true; break; }
+  for (int i = 0; i < MYO_PARAM_SLOTS; i++) if (!g_slot_used[i]) { b->slot = i; g_slot_used[i] = true; break; }
   if (b->slot < 0) { delete b; return fail(MYO_ERR_ARG, "too many live batches (8 constant-memory parameter slots)"); }
   memset(&b->F, 0, sizeof(b->F));
   try {
@@ -145,7 +160,8 @@ int myo_batch_create(const myo_model* m, int nworld, int nconmax, int njmax, myo
   } catch (const std::string& e) { g_slot_used[b->slot] = false; delete b; return fail(MYO_ERR_ARG, e); }
   {
     void* p = nullptr;
-    if (cudaMalloc(&p, myo_tpw_scratch_floats(b->L, nworld) * sizeof(float)) != cudaSuccess) { g_slot_used[b->slot] = false; delete b; return fail(MYO_ERR_CUDA, "cudaMalloc of the per-world scratch failed"); }
+    b->kern = pickVariant(nworld);
+    if (cudaMalloc(&p, b->kern->scratch_floats(b->L, nworld) * sizeof(float)) != cudaSuccess) { g_slot_used[b->slot] = false; delete b; return fail(MYO_ERR_CUDA, "cudaMalloc of the per-world scratch failed"); }
     b->owned.push_back(p); b->scratch = (float*)p;
   }
   // library-owned default state buffers (bind overrides them)
@@ -189,10 +205,11 @@ static int launch(myo_batch* b, int nsub, int forward_only, const int32_t* mask,
   int rc = checkReady(b);
   if (rc) return rc;
   if (b->dirty) {
-    if (myo_tpw_upload_params(b->slot, b->D, b->L, b->F, stream) != 0) return fail(MYO_ERR_CUDA, "parameter upload failed");
+    if (b->kern->upload(b->slot, b->D, b->L, b->F, stream) != 0) return fail(MYO_ERR_CUDA, "parameter upload failed");
     b->dirty = false;
   }
-  if (myo_tpw_launch_step(b->slot, b->L, b->nworld, nsub, forward_only, mask, do_reset, b->scratch, stream) != 0)
+  g_launches++;
+  if (b->kern->launch(b->slot, b->L, b->nworld, nsub, forward_only, mask, do_reset, b->scratch, stream) != 0)
     return fail(MYO_ERR_CUDA, std::string("kernel launch failed: ") + cudaGetErrorString(cudaGetLastError()));
   return MYO_OK;
 }
@@ -229,7 +246,8 @@ int myo_kat_quat(int n, const float* qa, const float* qb, float* prod, float* ma
   if (n <= 0 || !qa || !qb || !prod || !mat || !rotated) return fail(MYO_ERR_ARG, "bad argument");
   int ndev = 0;
   if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return fail(MYO_ERR_CUDA, "no CUDA device: libmyostep has no CPU fallback");
-  return myo_tpw_launch_quat_kat(n, qa, qb, prod, mat, rotated, stream) == 0 ? MYO_OK : fail(MYO_ERR_CUDA, "kernel launch failed");
+  g_launches++;
+  return myo_launch_quat_kat(n, qa, qb, prod, mat, rotated, stream) == 0 ? MYO_OK : fail(MYO_ERR_CUDA, "kernel launch failed");
 }
 
 }  // extern "C"

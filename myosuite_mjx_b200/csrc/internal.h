@@ -1,4 +1,4 @@
-// Internal declarations shared by plan.cu / kernels.cu / api.cu (not part of the public C ABI).
+// Internal declarations shared by plan.cu / team.cu / api.cu (not part of the public C ABI).
 #ifndef MYO_INTERNAL_H_
 #define MYO_INTERNAL_H_
 #include <string>
@@ -11,14 +11,27 @@ void myo_build_plan(const myo_model_desc& m, int nconmax_req, int njmax_req, Dev
 
 void myo_make_layout(DevModel& D, int nconmax_req, int njmax_req, SmemLayout& L);
 
-// lane = world kernel (tpw.cu): parameters live in constant-memory slots, one per live batch
-int myo_tpw_param_slots();
-size_t myo_tpw_scratch_floats(const SmemLayout& L, int nworld);   // floats of global scratch a batch needs
-int myo_tpw_upload_params(int slot, const DevModel& D, const SmemLayout& L, const FieldPtrs& F, void* stream);
-// nsub substeps (forward_only: mj_forward; do_reset: mj_resetData + mj_forward on the masked worlds) for nworld worlds
-int myo_tpw_launch_step(int slot, const SmemLayout& L, int nworld, int nsub, int forward_only, const int* reset_mask, int do_reset,
-                        float* scratch, void* stream);
-int myo_tpw_launch_quat_kat(int n, const float* qa, const float* qb, float* prod, float* mat, float* rotated, void* stream);
-int64_t myo_tpw_launch_counter();
+#define MYO_PARAM_SLOTS 8
+// The step kernel (team.cu) is compiled once per team width (lanes per world); every variant has its own
+// constant-memory parameter slots.
+struct TeamVariant {
+  int team;
+  int (*upload)(int slot, const DevModel& D, const SmemLayout& L, const FieldPtrs& F, void* stream);
+  // nsub substeps (forward_only: mj_forward; do_reset: mj_resetData + mj_forward on the masked worlds)
+  int (*launch)(int slot, const SmemLayout& L, int nworld, int nsub, int forward_only, const int* reset_mask, int do_reset,
+                float* scratch, void* stream);
+  size_t (*scratch_floats)(const SmemLayout& L, int nworld);
+};
+#define MYO_DECLARE_TEAM(T)                                                                                              \
+  int myo_team_upload_##T(int slot, const DevModel& D, const SmemLayout& L, const FieldPtrs& F, void* stream);           \
+  int myo_team_launch_##T(int slot, const SmemLayout& L, int nworld, int nsub, int forward_only, const int* reset_mask, \
+                          int do_reset, float* scratch, void* stream);                                                   \
+  size_t myo_team_scratch_##T(const SmemLayout& L, int nworld);
+MYO_DECLARE_TEAM(1)
+MYO_DECLARE_TEAM(2)
+MYO_DECLARE_TEAM(4)
+MYO_DECLARE_TEAM(8)
+MYO_DECLARE_TEAM(16)
+int myo_launch_quat_kat(int n, const float* qa, const float* qb, float* prod, float* mat, float* rotated, void* stream);
 
 #endif

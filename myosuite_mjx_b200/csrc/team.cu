@@ -137,6 +137,43 @@ struct SPI {
 };
 __device__ __forceinline__ SPI asInt(SP s) { SPI r; r.p = (int*)s.p; return r; }
 
+// A team of TEAM lanes works on one world; 32 / TEAM worlds share a warp.  Teams of one warp may diverge on data
+// (contacts, solver iterations), so every sync / shuffle names only the team's own lanes.
+struct Tm { int tl; unsigned mask; };
+#if TEAM == 1
+#define TSYNC() do { } while (0)
+#else
+#define TSYNC() __syncwarp(t.mask)
+#endif
+#define TFOR(i, n) for (int i = t.tl; i < (n); i += TEAM)
+__device__ __forceinline__ float teamSum(Tm t, float v) {
+#pragma unroll
+  for (int o = TEAM / 2; o > 0; o >>= 1) v += __shfl_xor_sync(t.mask, v, o);
+  return v;
+}
+__device__ __forceinline__ int teamSumI(Tm t, int v) {
+#pragma unroll
+  for (int o = TEAM / 2; o > 0; o >>= 1) v += __shfl_xor_sync(t.mask, v, o);
+  return v;
+}
+__device__ __forceinline__ bool teamAny(Tm t, bool p) {
+#if TEAM == 1
+  return p;
+#else
+  return (__ballot_sync(t.mask, p) & t.mask) != 0u;
+#endif
+}
+// exclusive prefix sum over the team's lanes (lane order), *total = team sum
+__device__ __forceinline__ int teamExclScan(Tm t, int v, int* total) {
+  int incl = v;
+#pragma unroll
+  for (int o = 1; o < TEAM; o <<= 1) { const int u = __shfl_up_sync(t.mask, incl, o, TEAM); if (t.tl >= o) incl += u; }
+  *total = __shfl_sync(t.mask, incl, TEAM - 1, TEAM);
+  return incl - v;
+}
+__device__ __forceinline__ float teamBcast(Tm t, float v, int src) { return __shfl_sync(t.mask, v, src, TEAM); }
+__device__ __forceinline__ int teamBcastI(Tm t, int v, int src) { return __shfl_sync(t.mask, v, src, TEAM); }
+
 // frame record in the per-world scratch: pos[3], quat[4], mat[9]
 #define FR_POS(sm, L, f) ((sm) + (L).frames + 16 * (f))
 #define FR_QUAT(sm, L, f) ((sm) + (L).frames + 16 * (f) + 3)
@@ -148,65 +185,66 @@ struct World { size_t w, nw; };
 #define OUTI(ptr, k) ((int*)(ptr))[(size_t)(k) * W.nw + W.w]
 
 // ------------------------------------------------------------------------------------------ kinematics
-__device__ __noinline__ void kinematics(int slot, SP sm) {
+__device__ __noinline__ void kinematics(int slot, SP sm, Tm t) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
-  {
+  if (t.tl == 0) {
     auto p = FR_POS(sm, L, 0);
     p[0] = p[1] = p[2] = 0.f; p[3] = 1.f; p[4] = p[5] = p[6] = 0.f;
     p[7] = 1.f; p[8] = 0.f; p[9] = 0.f; p[10] = 0.f; p[11] = 1.f; p[12] = 0.f; p[13] = 0.f; p[14] = 0.f; p[15] = 1.f;
   }
+  TSYNC();
   auto qpos = sm + L.qpos;
-  // #pragma unroll 1
-  for (int f = 1; f < D.nframe; f++) {   // frames are in depth-first order: parents come first
-    const int p = D.fr_parent[f], ja = D.fr_jntadr[f], jn = D.fr_jntnum[f];
-    f3 pos; f4 quat; float R[9];
-    if (jn == 1 && D.jnt_type[ja] == JNT_FREE) {
-      const int qa = D.jnt_qposadr[ja];
-      pos = ld3(qpos + qa);
-      quat = qnormalize(ld4(qpos + qa + 3));
-      st4(qpos + qa + 3, quat);
-      st3(sm + L.xanchor + 3 * ja, pos); st3(sm + L.xaxis + 3 * ja, ld3(D.jnt_axis + 3 * ja));
-    } else {
-      pos = ld3(FR_POS(sm, L, p)) + mulM(FR_MAT(sm, L, p), ld3(D.fr_pre_pos + 3 * f));
-      quat = qmul(ld4(FR_QUAT(sm, L, p)), ld4(D.fr_pre_quat + 4 * f));
-      q2m(R, quat);
-      // #pragma unroll 1
-      for (int j = ja; j < ja + jn; j++) {
-        const f3 lpos = ld3(D.jnt_pos + 3 * j), laxis = ld3(D.jnt_axis + 3 * j);
-        const f3 anchor = mulM(R, lpos) + pos, axis = mulM(R, laxis);
-        st3(sm + L.xanchor + 3 * j, anchor); st3(sm + L.xaxis + 3 * j, axis);
-        const int qa = D.jnt_qposadr[j];
-        const float d = qpos[qa] - D.qpos0[qa];
-        if (D.jnt_type[j] == JNT_SLIDE) pos = pos + axis * d;
-        else {
-          float sn, cs; sincos_(0.5f * d, &sn, &cs);
-          f4 ql; ql.w = cs; ql.x = laxis.x * sn; ql.y = laxis.y * sn; ql.z = laxis.z * sn;
-          quat = qmul(quat, ql);
-          q2m(R, quat);
-          pos = anchor - mulM(R, lpos);
+  for (int l = 0; l < D.nlevel; l++) {   // frames of one tree depth are independent
+    for (int idx = D.lvl_start[l] + t.tl; idx < D.lvl_start[l + 1]; idx += TEAM) {
+      const int f = D.lvl_frames[idx], p = D.fr_parent[f], ja = D.fr_jntadr[f], jn = D.fr_jntnum[f];
+      f3 pos; f4 quat; float R[9];
+      if (jn == 1 && D.jnt_type[ja] == JNT_FREE) {
+        const int qa = D.jnt_qposadr[ja];
+        pos = ld3(qpos + qa);
+        quat = qnormalize(ld4(qpos + qa + 3));
+        st4(qpos + qa + 3, quat);
+        st3(sm + L.xanchor + 3 * ja, pos); st3(sm + L.xaxis + 3 * ja, ld3(D.jnt_axis + 3 * ja));
+      } else {
+        pos = ld3(FR_POS(sm, L, p)) + mulM(FR_MAT(sm, L, p), ld3(D.fr_pre_pos + 3 * f));
+        quat = qmul(ld4(FR_QUAT(sm, L, p)), ld4(D.fr_pre_quat + 4 * f));
+        q2m(R, quat);
+        for (int j = ja; j < ja + jn; j++) {
+          const f3 lpos = ld3(D.jnt_pos + 3 * j), laxis = ld3(D.jnt_axis + 3 * j);
+          const f3 anchor = mulM(R, lpos) + pos, axis = mulM(R, laxis);
+          st3(sm + L.xanchor + 3 * j, anchor); st3(sm + L.xaxis + 3 * j, axis);
+          const int qa = D.jnt_qposadr[j];
+          const float d = qpos[qa] - D.qpos0[qa];
+          if (D.jnt_type[j] == JNT_SLIDE) pos = pos + axis * d;
+          else {
+            float sn, cs; sincos_(0.5f * d, &sn, &cs);
+            f4 ql; ql.w = cs; ql.x = laxis.x * sn; ql.y = laxis.y * sn; ql.z = laxis.z * sn;
+            quat = qmul(quat, ql);
+            q2m(R, quat);
+            pos = anchor - mulM(R, lpos);
+          }
         }
       }
-    }
-    quat = qnormalize(quat);
-    q2m(R, quat);
-    auto o = FR_POS(sm, L, f);
-    st3(o, pos); st4(o + 3, quat);
+      quat = qnormalize(quat);
+      q2m(R, quat);
+      auto o = FR_POS(sm, L, f);
+      st3(o, pos); st4(o + 3, quat);
 #pragma unroll
-    for (int k = 0; k < 9; k++) o[7 + k] = R[k];
+      for (int k = 0; k < 9; k++) o[7 + k] = R[k];
+    }
+    TSYNC();
   }
 }
 
 // composite inertia of every frame about its tree's centre of mass, motion axes (mj_comPos over weld groups)
-__device__ __noinline__ void comPos(int slot, SP sm) {
+__device__ __noinline__ void comPos(int slot, SP sm, Tm t) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
   auto cin = sm + L.cinert;
-  // #pragma unroll 1
-  for (int f = 0; f < D.nframe; f++) {
+  TFOR(f, D.nframe) {
     f3 cw = ld3(FR_POS(sm, L, f)) + mulM(FR_MAT(sm, L, f), ld3(D.fr_com + 3 * f));
     st3(cin + 10 * f + 6, cw); cin[10 * f + 9] = D.fr_mass[f];
   }
-  // #pragma unroll 1
-  for (int r = 0; r < D.nroot; r++) {
+  TSYNC();
+  TFOR(r, D.nroot) {
     f3 acc = ld3(D.root_const + 4 * r);
     const float M = D.root_const[4 * r + 3];
     // #pragma unroll 1
@@ -214,8 +252,8 @@ __device__ __noinline__ void comPos(int slot, SP sm) {
     if (M < MINVAL) acc = mk3(0.f, 0.f, 0.f); else acc = acc * (1.f / M);
     st3(sm + L.rootcom + 3 * r, acc);
   }
-  // #pragma unroll 1
-  for (int f = 0; f < D.nframe; f++) {
+  TSYNC();
+  TFOR(f, D.nframe) {
     auto c = cin + 10 * f;
     if (f == 0) { for (int k = 0; k < 10; k++) c[k] = 0.f; continue; }
     auto R = FR_MAT(sm, L, f);
@@ -236,8 +274,7 @@ __device__ __noinline__ void comPos(int slot, SP sm) {
     c[2] = zz + m * (off.x * off.x + off.y * off.y); c[3] = xy - m * off.x * off.y; c[4] = xz - m * off.x * off.z;
     c[5] = yz - m * off.y * off.z; c[6] = m * off.x; c[7] = m * off.y; c[8] = m * off.z;
   }
-  // #pragma unroll 1
-  for (int j = 0; j < D.njnt; j++) {
+  TFOR(j, D.njnt) {
     const int f = D.jnt_frame[j], da = D.jnt_dofadr[j];
     const f3 off = ld3(sm + L.rootcom + 3 * D.fr_root[f]) - ld3(sm + L.xanchor + 3 * j);
     const f3 axis = ld3(sm + L.xaxis + 3 * j);
@@ -257,20 +294,20 @@ __device__ __noinline__ void comPos(int slot, SP sm) {
       st3(cd, axis); st3(cd + 3, cross(axis, off));
     }
   }
+  TSYNC();
 }
 
 // ------------------------------------------------------------------------------------------ mjData position outputs
 // Written straight to global memory (struct-of-arrays, coalesced across the warp's worlds); nothing here feeds the dynamics.
-__device__ __noinline__ void writePositionOutputs(int slot, int fslot, SP sm, World W) {
+__device__ __noinline__ void writePositionOutputs(int slot, int fslot, SP sm, Tm t, World W) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L; const FieldPtrs& F = tP[fslot].F;
   void* xpos = F.p[MYO_F_XPOS]; void* xquat = F.p[MYO_F_XQUAT]; void* xmat = F.p[MYO_F_XMAT];
   void* xipos = F.p[MYO_F_XIPOS]; void* ximat = F.p[MYO_F_XIMAT]; void* cinert = F.p[MYO_F_CINERT];
   void* scom = F.p[MYO_F_SUBTREE_COM]; void* crb = F.p[MYO_F_CRB];
   const int nb = D.nbody;
-  auto tb = sm + L.tmpbody;   // [nbody][13]: mass-weighted com accumulators (3) + body-level cinert (10)
+  auto tb = sm + L.tmpbody;   // [nbody][13]: m * xipos (3) + body-level cinert (10)
   if (xpos || xquat || xmat || xipos || ximat || cinert || scom || crb) {
-    // #pragma unroll 1
-    for (int b = 0; b < nb; b++) {
+    TFOR(b, nb) {
       const int f = D.body_frame[b];
       auto R = FR_MAT(sm, L, f);
       const f3 pos = ld3(FR_POS(sm, L, f)) + mulM(R, ld3(D.body_off_pos + 3 * b));
@@ -286,15 +323,14 @@ __device__ __noinline__ void writePositionOutputs(int slot, int fslot, SP sm, Wo
       const f3 ip = pos + mulM(M, ld3(D.body_ipos + 3 * b));
       if (xipos) { OUTF(xipos, 3 * b) = ip.x; OUTF(xipos, 3 * b + 1) = ip.y; OUTF(xipos, 3 * b + 2) = ip.z; }
       const float m = D.body_mass[b];
-      auto t = tb + 13 * b;
-      const bool massless = D.body_subtreemass[b] < MINVAL;   // MuJoCo: subtree_com of a massless subtree = xipos
-      t[0] = massless ? ip.x : m * ip.x; t[1] = massless ? ip.y : m * ip.y; t[2] = massless ? ip.z : m * ip.z;
+      auto tt = tb + 13 * b;
+      tt[0] = m * ip.x; tt[1] = m * ip.y; tt[2] = m * ip.z;
       if (ximat || cinert || crb) {
         float IM[9]; mulMM(IM, M, D.body_imat + 9 * b);
         if (ximat)
 #pragma unroll
           for (int k = 0; k < 9; k++) OUTF(ximat, 9 * b + k) = IM[k];
-        auto c = t + 3;
+        float c[10];
         if (b == 0) { for (int k = 0; k < 10; k++) c[k] = 0.f; }
         else {
           const float i0 = D.body_inertia[3 * b], i1 = D.body_inertia[3 * b + 1], i2 = D.body_inertia[3 * b + 2];
@@ -307,41 +343,52 @@ __device__ __noinline__ void writePositionOutputs(int slot, int fslot, SP sm, Wo
           c[5] = IM[3] * IM[6] * i0 + IM[4] * IM[7] * i1 + IM[5] * IM[8] * i2 - m * off.y * off.z;
           c[6] = m * off.x; c[7] = m * off.y; c[8] = m * off.z; c[9] = m;
         }
-        if (cinert)
 #pragma unroll
-          for (int k = 0; k < 10; k++) OUTF(cinert, 10 * b + k) = c[k];
+        for (int k = 0; k < 10; k++) { tt[3 + k] = c[k]; if (cinert) OUTF(cinert, 10 * b + k) = c[k]; }
       }
     }
     if (scom || crb) {
-      // subtree sums by one backward sweep (bodies are depth-first: parent index < child index)
-      // #pragma unroll 1
-      for (int b = nb - 1; b >= 0; b--) {
-        auto t = tb + 13 * b;
+      TSYNC();
+      // subtree sums: bodies are depth-first, a subtree is the contiguous range [b, body_subend[b])
+      TFOR(b, nb) {
+        const int e = D.body_subend[b];
         if (scom) {
           const float Ms = D.body_subtreemass[b];
-          const f3 c = Ms < MINVAL ? mk3(t[0], t[1], t[2]) : mk3(t[0], t[1], t[2]) * (1.f / Ms);
+          f3 c;
+          if (Ms < MINVAL) {   // MuJoCo: subtree_com of a massless subtree = xipos
+            const int f = D.body_frame[b];
+            auto R = FR_MAT(sm, L, f);
+            float M[9]; mulMM(M, R, D.body_off_mat + 9 * b);
+            c = ld3(FR_POS(sm, L, f)) + mulM(R, ld3(D.body_off_pos + 3 * b)) + mulM(M, ld3(D.body_ipos + 3 * b));
+          } else {
+            f3 acc = mk3(0.f, 0.f, 0.f);
+            for (int q = b; q < e; q++) acc = acc + ld3(tb + 13 * q);
+            c = acc * (1.f / Ms);
+          }
           OUTF(scom, 3 * b) = c.x; OUTF(scom, 3 * b + 1) = c.y; OUTF(scom, 3 * b + 2) = c.z;
         }
-        if (crb)
+        if (crb) {
+          float acc[10];
 #pragma unroll
-          for (int k = 0; k < 10; k++) OUTF(crb, 10 * b + k) = b > 0 ? t[3 + k] : 0.f;
-        if (b > 0) {
-          auto tp = tb + 13 * D.body_parent[b];
-          if (!(D.body_subtreemass[b] < MINVAL)) for (int k = 0; k < 3; k++) tp[k] += t[k];
-          if (crb && D.body_parent[b] > 0) for (int k = 3; k < 13; k++) tp[k] += t[k];
+          for (int k = 0; k < 10; k++) acc[k] = 0.f;
+          if (b > 0)
+            for (int q = b; q < e; q++)
+#pragma unroll
+              for (int k = 0; k < 10; k++) acc[k] += tb[13 * q + 3 + k];
+#pragma unroll
+          for (int k = 0; k < 10; k++) OUTF(crb, 10 * b + k) = acc[k];
         }
       }
     }
   }
   void* xa = F.p[MYO_F_XANCHOR]; void* xx = F.p[MYO_F_XAXIS];
-  if (xa) for (int i = 0; i < 3 * D.njnt; i++) OUTF(xa, i) = sm[L.xanchor + i];
-  if (xx) for (int i = 0; i < 3 * D.njnt; i++) OUTF(xx, i) = sm[L.xaxis + i];
+  if (xa) TFOR(i, 3 * D.njnt) OUTF(xa, i) = sm[L.xanchor + i];
+  if (xx) TFOR(i, 3 * D.njnt) OUTF(xx, i) = sm[L.xaxis + i];
   void* cd = F.p[MYO_F_CDOF];
-  if (cd) for (int i = 0; i < 6 * D.nv; i++) OUTF(cd, i) = sm[L.cdof + i];
+  if (cd) TFOR(i, 6 * D.nv) OUTF(cd, i) = sm[L.cdof + i];
   void* gp = F.p[MYO_F_GEOM_XPOS]; void* gm = F.p[MYO_F_GEOM_XMAT];
   if (gp || gm) {
-    // #pragma unroll 1
-    for (int g = 0; g < D.ngeom; g++) {
+    TFOR(g, D.ngeom) {
       const int f = D.geom_frame[g];
       auto R = FR_MAT(sm, L, f);
       if (gp) {
@@ -357,22 +404,23 @@ __device__ __noinline__ void writePositionOutputs(int slot, int fslot, SP sm, Wo
   }
   void* sp = F.p[MYO_F_SITE_XPOS]; void* smt = F.p[MYO_F_SITE_XMAT];
   if (sp || smt) {
-    // #pragma unroll 1
-    for (int s = 0; s < D.nsite; s++) {
-      const int f = D.site_frame[s];
+    TFOR(q, D.nsite) {
+      const int f = D.site_frame[q];
       auto R = FR_MAT(sm, L, f);
       if (sp) {
-        const f3 p = ld3(FR_POS(sm, L, f)) + mulM(R, ld3(D.site_lpos + 3 * s));
-        OUTF(sp, 3 * s) = p.x; OUTF(sp, 3 * s + 1) = p.y; OUTF(sp, 3 * s + 2) = p.z;
+        const f3 p = ld3(FR_POS(sm, L, f)) + mulM(R, ld3(D.site_lpos + 3 * q));
+        OUTF(sp, 3 * q) = p.x; OUTF(sp, 3 * q + 1) = p.y; OUTF(sp, 3 * q + 2) = p.z;
       }
       if (smt) {
-        float M[9]; mulMM(M, R, D.site_lmat + 9 * s);
+        float M[9]; mulMM(M, R, D.site_lmat + 9 * q);
 #pragma unroll
-        for (int k = 0; k < 9; k++) OUTF(smt, 9 * s + k) = M[k];
+        for (int k = 0; k < 9; k++) OUTF(smt, 9 * q + k) = M[k];
       }
     }
   }
+  TSYNC();   // tmpbody overlays the tendon stage's scratch
 }
+
 // ------------------------------------------------------------------------------------------ tendon wrapping (mju_wrap)
 __device__ __forceinline__ bool segIntersect(const float* p1, const float* p2, const float* p3, const float* p4) {
   const float det = (p4[1] - p3[1]) * (p2[0] - p1[0]) - (p4[0] - p3[0]) * (p2[1] - p1[1]);
@@ -511,10 +559,9 @@ __device__ __noinline__ float wrapGeom(f3 x0, f3 x1, f3 gpos, const float* gmat,
 }
 
 // mj_tendon: path lengths + sparse moment arms
-__device__ __noinline__ void tendons(int slot, int fslot, SP sm, World W) {
+__device__ __noinline__ void tendons(int slot, int fslot, SP sm, Tm t, World W) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L; const FieldPtrs& F = tP[fslot].F;
-  // #pragma unroll 1
-  for (int u = 0; u < D.nunit; u++) {
+  TFOR(u, D.nunit) {
     const int s0 = D.unit_s0[u], s1 = D.unit_s1[u], g = D.unit_geom[u];
     const int f0 = D.site_frame[s0], f1 = D.site_frame[s1];
     const f3 p0 = ld3(FR_POS(sm, L, f0)) + mulM(FR_MAT(sm, L, f0), ld3(D.site_lpos + 3 * s0));
@@ -543,10 +590,9 @@ __device__ __noinline__ void tendons(int slot, int fslot, SP sm, World W) {
     sm[L.ulen + u] = len / D.unit_div[u];
     sm[L.uwrap + u] = wlen < 0.f ? 0.f : 1.f;
   }
-  // #pragma unroll 1
-  for (int n = 0; n < D.nnz; n++) {
+  TSYNC();
+  TFOR(n, D.nnz) {
     float acc = 0.f;
-    // #pragma unroll 1
     for (int e = D.nz_estart[n]; e < D.nz_estart[n + 1]; e++) {
       const int kind = D.ent_kind[e];
       if (kind != ENT_ALWAYS) {
@@ -561,188 +607,174 @@ __device__ __noinline__ void tendons(int slot, int fslot, SP sm, World W) {
     }
     sm[L.tenJ + n] = acc;
   }
-  // #pragma unroll 1
-  for (int t = 0; t < D.nten; t++) {
+  TFOR(k, D.nten) {
     float acc = 0.f;
-    // #pragma unroll 1
-    for (int u = D.ten_ustart[t]; u < D.ten_ustart[t + 1]; u++) acc += sm[L.ulen + u];
-    sm[L.tenlen + t] = acc;
+    for (int u = D.ten_ustart[k]; u < D.ten_ustart[k + 1]; u++) acc += sm[L.ulen + u];
+    sm[L.tenlen + k] = acc;
   }
+  TSYNC();
   void* tl = F.p[MYO_F_TEN_LENGTH]; void* tj = F.p[MYO_F_TEN_J];
-  if (tl) for (int t = 0; t < D.nten; t++) OUTF(tl, t) = sm[L.tenlen + t];
+  if (tl) TFOR(k, D.nten) OUTF(tl, k) = sm[L.tenlen + k];
   if (tj) {
-    // #pragma unroll 1
-    for (int t = 0; t < D.nten; t++) {   // dense row = zeros with the sparse entries (sorted by dof) merged in
-      int k = D.ten_nzstart[t];
-      const int kend = D.ten_nzstart[t + 1];
-      // #pragma unroll 1
+    TFOR(k, D.nten) {   // dense row = zeros with the sparse entries (sorted by dof) merged in
+      int q = D.ten_nzstart[k];
+      const int qend = D.ten_nzstart[k + 1];
       for (int i = 0; i < D.nv; i++) {
         float v = 0.f;
-        if (k < kend && D.nz_dof[k] == i) { v = sm[L.tenJ + k]; k++; }
-        OUTF(tj, t * D.nv + i) = v;
+        if (q < qend && D.nz_dof[q] == i) { v = sm[L.tenJ + q]; q++; }
+        OUTF(tj, k * D.nv + i) = v;
       }
     }
   }
 }
 
 // ------------------------------------------------------------------------------------------ inertia: mj_crb, mj_factorM, mj_solveM
-// sparse L^T D L in place over the dof-tree pattern (row i: entries M[i, i], M[i, parent(i)], ... at dof_Madr[i] + s)
-__device__ __noinline__ void factorLDL(int slot, SP LD, SP dinv) {
+// sparse L^T D L in place over the dof-tree pattern; one precomputed multiply-subtract list per column
+__device__ __noinline__ void factorLDL(int slot, SP LD, SP dinv, Tm t) {
   const DevModel& D = tP[slot].D;
   const int nv = D.nv;
-  // #pragma unroll 1
   for (int pos = 0; pos < nv; pos++) {
     const int k = nv - 1 - pos, akk = D.dof_Madr[k];
     const float inv = 1.f / LD[akk];
-    // #pragma unroll 1
-    for (int o = D.ldl_start[pos]; o < D.ldl_start[pos + 1]; o++) LD[D.ldl_dst[o]] -= LD[D.ldl_a[o]] * LD[D.ldl_b[o]] * inv;
+    for (int o = D.ldl_start[pos] + t.tl; o < D.ldl_start[pos + 1]; o += TEAM) LD[D.ldl_dst[o]] -= LD[D.ldl_a[o]] * LD[D.ldl_b[o]] * inv;
+    TSYNC();
     const int d = D.dof_rowlen[k];
-    // #pragma unroll 1
-    for (int s = 1; s < d; s++) LD[akk + s] *= inv;
-    dinv[k] = inv;
+    for (int q = 1 + t.tl; q < d; q += TEAM) LD[akk + q] *= inv;
+    if (t.tl == 0) dinv[k] = inv;
+    TSYNC();
   }
 }
-// x <- (L^T D L)^-1 x
-__device__ __noinline__ void solveLDL(int slot, SP LD, SP dinv, SP x) {
+// x <- (L^T D L)^-1 x, by dof-tree levels
+__device__ __noinline__ void solveLDL(int slot, SP LD, SP dinv, SP x, Tm t) {
   const DevModel& D = tP[slot].D;
-  const int nv = D.nv;
-  // x <- L^-T x : column sweep from the last dof, scattering into the ancestors
-  // #pragma unroll 1
-  for (int i = nv - 1; i >= 0; i--) {
-    const int a = D.dof_Madr[i], d = D.dof_rowlen[i];
-    const float xi = x[i];
-    // #pragma unroll 1
-    for (int s = 1; s < d; s++) { const int j = D.M_col[a + s]; x[j] = fmaf(-LD[a + s], xi, x[j]); }
+  for (int l = D.ndlevel - 1; l >= 0; l--) {
+    for (int idx = D.dlvl_start[l] + t.tl; idx < D.dlvl_start[l + 1]; idx += TEAM) {
+      const int j = D.dlvl_dofs[idx];
+      float acc = x[j];
+      for (int e = D.desc_start[j]; e < D.desc_start[j + 1]; e++) acc = fmaf(-LD[D.desc_idx[e]], x[D.desc_dof[e]], acc);
+      x[j] = acc;
+    }
+    TSYNC();
   }
-  // #pragma unroll 1
-  for (int i = 0; i < nv; i++) x[i] *= dinv[i];
-  // x <- L^-1 x : rows in increasing order, gathering from the ancestors
-  // #pragma unroll 1
-  for (int i = 0; i < nv; i++) {
-    const int a = D.dof_Madr[i], d = D.dof_rowlen[i];
-    float acc = x[i];
-    // #pragma unroll 1
-    for (int s = 1; s < d; s++) acc = fmaf(-LD[a + s], x[D.M_col[a + s]], acc);
-    x[i] = acc;
+  TFOR(i, D.nv) x[i] *= dinv[i];
+  TSYNC();
+  for (int l = 1; l < D.ndlevel; l++) {
+    for (int idx = D.dlvl_start[l] + t.tl; idx < D.dlvl_start[l + 1]; idx += TEAM) {
+      const int i = D.dlvl_dofs[idx], a = D.dof_Madr[i], d = D.dof_rowlen[i];
+      float acc = x[i];
+      for (int q = 1; q < d; q++) acc = fmaf(-LD[a + q], x[D.M_col[a + q]], acc);
+      x[i] = acc;
+    }
+    TSYNC();
   }
 }
-__device__ __noinline__ void inertia(int slot, int fslot, SP sm, World W) {
+__device__ __noinline__ void inertia(int slot, int fslot, SP sm, Tm t, World W) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L; const FieldPtrs& F = tP[fslot].F;
   const int nv = D.nv;
-  // composite inertia of each frame's subtree: backward sweep over the depth-first frame order
-  // #pragma unroll 1
-  for (int i = 0; i < 10 * D.nframe; i++) sm[L.crb + i] = sm[L.cinert + i];
-  // #pragma unroll 1
-  for (int f = D.nframe - 1; f >= 1; f--) {
-    const int p = D.fr_parent[f];
-    if (p > 0)
+  // composite inertia of each frame's subtree (frames are depth-first: subtree = contiguous range)
+  TFOR(i, 10 * D.nframe) {
+    const int f = i / 10, k = i - 10 * f;
+    float acc = 0.f;
+    if (f > 0) for (int g = f; g < D.fr_subend[f]; g++) acc += sm[L.cinert + 10 * g + k];
+    sm[L.crb + i] = acc;
+  }
+  TSYNC();
+  auto f6 = sm + L.cdof_dot;  // scratch until the velocity stage
+  TFOR(i, nv) {
+    float r[6];
+    inertMulVec(r, sm + L.crb + 10 * D.dof_frame[i], sm + L.cdof + 6 * i);
 #pragma unroll
-      for (int k = 0; k < 10; k++) sm[L.crb + 10 * p + k] += sm[L.crb + 10 * f + k];
+    for (int k = 0; k < 6; k++) f6[6 * i + k] = r[k];
   }
-  // #pragma unroll 1
-  for (int i = 0; i < nv; i++) {
-    float f6[6];
-    inertMulVec(f6, sm + L.crb + 10 * D.dof_frame[i], sm + L.cdof + 6 * i);
-    const int a = D.dof_Madr[i], d = D.dof_rowlen[i];
-    // #pragma unroll 1
-    for (int s = 0; s < d; s++) {
-      auto c = sm + L.cdof + 6 * D.M_col[a + s];
-      float v = c[0] * f6[0] + c[1] * f6[1] + c[2] * f6[2] + c[3] * f6[3] + c[4] * f6[4] + c[5] * f6[5];
-      if (s == 0) v += D.dof_armature[i];
-      sm[L.qM + a + s] = v; sm[L.qLD + a + s] = v;
-    }
+  TSYNC();
+  TFOR(e, D.nM) {
+    const int r = D.M_row[e], c = D.M_col[e];
+    auto a = sm + L.cdof + 6 * c; auto b = f6 + 6 * r;
+    float v = a[0] * b[0] + a[1] * b[1] + a[2] * b[2] + a[3] * b[3] + a[4] * b[4] + a[5] * b[5];
+    if (r == c) v += D.dof_armature[r];
+    sm[L.qM + e] = v; sm[L.qLD + e] = v;
   }
-  factorLDL(slot, sm + L.qLD, sm + L.qLDinv);
+  TSYNC();
+  factorLDL(slot, sm + L.qLD, sm + L.qLDinv, t);
   void* qMo = F.p[MYO_F_QM]; void* qLDo = F.p[MYO_F_QLD]; void* qdi = F.p[MYO_F_QLDIAGINV];
   if (qMo || qLDo) {
-    // #pragma unroll 1
-    for (int i = 0; i < nv * nv; i++) { if (qMo) OUTF(qMo, i) = 0.f; if (qLDo) OUTF(qLDo, i) = 0.f; }
-    // #pragma unroll 1
-    for (int e = 0; e < D.nM; e++) {
+    TFOR(i, nv * nv) { if (qMo) OUTF(qMo, i) = 0.f; if (qLDo) OUTF(qLDo, i) = 0.f; }
+    TSYNC();
+    TFOR(e, D.nM) {
       const int r = D.M_row[e], c = D.M_col[e];
       if (qMo) { OUTF(qMo, r * nv + c) = sm[L.qM + e]; OUTF(qMo, c * nv + r) = sm[L.qM + e]; }
       if (qLDo) OUTF(qLDo, r * nv + c) = sm[L.qLD + e];
     }
   }
-  if (qdi) for (int i = 0; i < nv; i++) OUTF(qdi, i) = sm[L.qLDinv + i];
+  if (qdi) TFOR(i, nv) OUTF(qdi, i) = sm[L.qLDinv + i];
 }
 
 // ------------------------------------------------------------------------------------------ mj_fwdVelocity
-__device__ __noinline__ void velocity(int slot, int fslot, SP sm, World W) {
+__device__ __noinline__ void velocity(int slot, int fslot, SP sm, Tm t, World W) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L; const FieldPtrs& F = tP[fslot].F;
   const int nv = D.nv;
   auto qvel = sm + L.qvel;
-  // #pragma unroll 1
-  for (int t = 0; t < D.nten; t++) {
+  TFOR(k, D.nten) {
     float acc = 0.f;
-    // #pragma unroll 1
-    for (int n = D.ten_nzstart[t]; n < D.ten_nzstart[t + 1]; n++) acc = fmaf(sm[L.tenJ + n], qvel[D.nz_dof[n]], acc);
-    sm[L.tenvel + t] = acc;
+    for (int n = D.ten_nzstart[k]; n < D.ten_nzstart[k + 1]; n++) acc = fmaf(sm[L.tenJ + n], qvel[D.nz_dof[n]], acc);
+    sm[L.tenvel + k] = acc;
   }
-  // body velocities down the tree (all motion axes are expressed about the tree's centre of mass), with
-  // cdof_dot = cvel(before this dof) x cdof on the way
+  // body velocities: sum of the ancestor dof motions (all expressed about the tree's centre of mass)
+  TFOR(f, D.nframe) {
+    float v[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    if (f > 0) {
+      const int last = D.fr_dofadr[f] + D.fr_dofnum[f] - 1, a = D.dof_Madr[last], d = D.dof_rowlen[last];
+      for (int q = d - 1; q >= 0; q--) {
+        const int j = D.M_col[a + q]; const float qv = qvel[j]; auto cd = sm + L.cdof + 6 * j;
+#pragma unroll
+        for (int k = 0; k < 6; k++) v[k] = fmaf(cd[k], qv, v[k]);
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < 6; k++) sm[L.cvel + 6 * f + k] = v[k];
+  }
+  TFOR(i, nv) {
+    const int pc = D.dof_prevcount[i], a = D.dof_Madr[i], d = D.dof_rowlen[i];
+    auto out = sm + L.cdof_dot + 6 * i;
+    if (pc < 0) { for (int k = 0; k < 6; k++) out[k] = 0.f; continue; }
+    float v[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (int q = d - 1; q >= pc; q--) {
+      const int j = D.M_col[a + q]; const float qv = qvel[j]; auto cd = sm + L.cdof + 6 * j;
+#pragma unroll
+      for (int k = 0; k < 6; k++) v[k] = fmaf(cd[k], qv, v[k]);
+    }
+    float r[6];
+    crossMotion(r, v, sm + L.cdof + 6 * i);
+#pragma unroll
+    for (int k = 0; k < 6; k++) out[k] = r[k];
+  }
+  TSYNC();
   const bool grav = !(D.disableflags & DSBL_GRAVITY);
-  // #pragma unroll 1
-  for (int k = 0; k < 6; k++) { sm[L.cvel + k] = 0.f; sm[L.cacc + k] = 0.f; }
-  // #pragma unroll 1
-  for (int f = 1; f < D.nframe; f++) {
-    const int p = D.fr_parent[f];
-    float v[6], a6[6];
+  TFOR(f, D.nframe) {
+    if (f == 0) { for (int k = 0; k < 6; k++) sm[L.cacc + k] = 0.f; continue; }
+    float a6[6] = {0.f, 0.f, 0.f, grav ? -D.gravity[0] : 0.f, grav ? -D.gravity[1] : 0.f, grav ? -D.gravity[2] : 0.f};
+    const int last = D.fr_dofadr[f] + D.fr_dofnum[f] - 1, a = D.dof_Madr[last], d = D.dof_rowlen[last];
+    for (int q = d - 1; q >= 0; q--) {
+      const int j = D.M_col[a + q]; const float qv = qvel[j]; auto cd = sm + L.cdof_dot + 6 * j;
 #pragma unroll
-    for (int k = 0; k < 6; k++) v[k] = sm[L.cvel + 6 * p + k];
-    if (p == 0) { a6[0] = a6[1] = a6[2] = 0.f; a6[3] = grav ? -D.gravity[0] : 0.f; a6[4] = grav ? -D.gravity[1] : 0.f; a6[5] = grav ? -D.gravity[2] : 0.f; }
-    else {
-#pragma unroll
-      for (int k = 0; k < 6; k++) a6[k] = sm[L.cacc + 6 * p + k];
+      for (int k = 0; k < 6; k++) a6[k] = fmaf(cd[k], qv, a6[k]);
     }
-    const int da = D.fr_dofadr[f], dn = D.fr_dofnum[f];
-    const bool isfree = D.jnt_type[D.fr_jntadr[f]] == JNT_FREE;
-    float vstart[6];
-#pragma unroll
-    for (int k = 0; k < 6; k++) vstart[k] = v[k];
-    // #pragma unroll 1
-    for (int i = da; i < da + dn; i++) {
-      auto cd = sm + L.cdof + 6 * i;
-      auto cdd = sm + L.cdof_dot + 6 * i;
-      const int pc = D.dof_prevcount[i];
-      // free joint: translations have zero cdof_dot, rotations use the velocity after the translational dofs
-      if (pc < 0) { for (int k = 0; k < 6; k++) cdd[k] = 0.f; }
-      else if (isfree) {
-        if (i == da + 3) for (int k = 0; k < 6; k++) vstart[k] = v[k];
-        crossMotion(cdd, vstart, cd);
-      } else crossMotion(cdd, v, cd);
-      const float qv = qvel[i];
-#pragma unroll
-      for (int k = 0; k < 6; k++) { v[k] = fmaf(cd[k], qv, v[k]); a6[k] = fmaf(cdd[k], qv, a6[k]); }
-    }
-#pragma unroll
-    for (int k = 0; k < 6; k++) { sm[L.cvel + 6 * f + k] = v[k]; sm[L.cacc + 6 * f + k] = a6[k]; }
-  }
-  // body forces cfrc = I a + v x* (I v), accumulated up the tree; bias = cdof . cfrc(subtree)
-  auto cfrc = sm + L.cacc;   // in place: cacc[f] becomes the body force, a frame's acceleration is not needed after it
-  // #pragma unroll 1
-  for (int f = 0; f < D.nframe; f++) {
-    auto o = cfrc + 6 * f;
-    if (f == 0) { for (int k = 0; k < 6; k++) o[k] = 0.f; continue; }
     float Ia[6], Iv[6], cf[6];
-    inertMulVec(Ia, sm + L.cinert + 10 * f, sm + L.cacc + 6 * f);
+    inertMulVec(Ia, sm + L.cinert + 10 * f, a6);
     inertMulVec(Iv, sm + L.cinert + 10 * f, sm + L.cvel + 6 * f);
     crossForce(cf, sm + L.cvel + 6 * f, Iv);
 #pragma unroll
-    for (int k = 0; k < 6; k++) o[k] = Ia[k] + cf[k];
+    for (int k = 0; k < 6; k++) sm[L.cacc + 6 * f + k] = Ia[k] + cf[k];   // cacc now holds the body force cfrc
   }
-  // #pragma unroll 1
-  for (int f = D.nframe - 1; f >= 1; f--) {
-    const int p = D.fr_parent[f];
-    if (p > 0)
-#pragma unroll
-      for (int k = 0; k < 6; k++) cfrc[6 * p + k] += cfrc[6 * f + k];
-  }
+  TSYNC();
   const bool passive_on = !(D.disableflags & DSBL_PASSIVE);
   void* osp = F.p[MYO_F_QFRC_SPRING]; void* odm = F.p[MYO_F_QFRC_DAMPER]; void* ops = F.p[MYO_F_QFRC_PASSIVE]; void* obi = F.p[MYO_F_QFRC_BIAS];
-  // #pragma unroll 1
-  for (int i = 0; i < nv; i++) {
-    auto acc = cfrc + 6 * D.dof_frame[i];
+  TFOR(i, nv) {
+    const int f = D.dof_frame[i];
+    float acc[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (int g = f; g < D.fr_subend[f]; g++)
+#pragma unroll
+      for (int k = 0; k < 6; k++) acc[k] += sm[L.cacc + 6 * g + k];
     auto cd = sm + L.cdof + 6 * i;
     const float bias = cd[0] * acc[0] + cd[1] * acc[1] + cd[2] * acc[2] + cd[3] * acc[3] + cd[4] * acc[4] + cd[5] * acc[5];
     sm[L.bias + i] = bias;
@@ -753,16 +785,15 @@ __device__ __noinline__ void velocity(int slot, int fslot, SP sm, World W) {
       if (k != 0.f && D.jnt_type[j] >= JNT_SLIDE) spring = -k * (sm[L.qpos + D.jnt_qposadr[j]] - D.qpos_spring[D.jnt_qposadr[j]]);
       damper = -D.dof_damping[i] * qvel[i];
       if (D.any_tendon_passive)
-        // #pragma unroll 1
         for (int c = D.col_start[i]; c < D.col_start[i + 1]; c++) {
-          const int n = D.col_nz[c], t = D.nz_tendon[n];
-          const float ks = D.ten_stiffness[t], kd = D.ten_damping[t], len = sm[L.tenlen + t];
+          const int n = D.col_nz[c], tn = D.nz_tendon[n];
+          const float ks = D.ten_stiffness[tn], kd = D.ten_damping[tn], len = sm[L.tenlen + tn];
           if (ks > 0.f) {
-            const float lo = D.ten_lengthspring[2 * t], hi = D.ten_lengthspring[2 * t + 1];
+            const float lo = D.ten_lengthspring[2 * tn], hi = D.ten_lengthspring[2 * tn + 1];
             const float fs = len > hi ? ks * (hi - len) : (len < lo ? ks * (lo - len) : 0.f);
             spring += sm[L.tenJ + n] * fs;
           }
-          if (kd > 0.f) damper -= kd * sm[L.tenvel + t] * sm[L.tenJ + n];
+          if (kd > 0.f) damper -= kd * sm[L.tenvel + tn] * sm[L.tenJ + n];
         }
     }
     sm[L.passive + i] = spring + damper;
@@ -772,10 +803,12 @@ __device__ __noinline__ void velocity(int slot, int fslot, SP sm, World W) {
     if (obi) OUTF(obi, i) = bias;
   }
   void* o;
-  if ((o = F.p[MYO_F_TEN_VELOCITY])) for (int t = 0; t < D.nten; t++) OUTF(o, t) = sm[L.tenvel + t];
-  if ((o = F.p[MYO_F_CDOF_DOT])) for (int i = 0; i < 6 * nv; i++) OUTF(o, i) = sm[L.cdof_dot + i];
-  if ((o = F.p[MYO_F_CVEL])) for (int b = 0; b < D.nbody; b++) for (int k = 0; k < 6; k++) OUTF(o, 6 * b + k) = sm[L.cvel + 6 * D.body_frame[b] + k];
+  if ((o = F.p[MYO_F_TEN_VELOCITY])) TFOR(k, D.nten) OUTF(o, k) = sm[L.tenvel + k];
+  if ((o = F.p[MYO_F_CDOF_DOT])) TFOR(i, 6 * nv) OUTF(o, i) = sm[L.cdof_dot + i];
+  if ((o = F.p[MYO_F_CVEL])) TFOR(i, 6 * D.nbody) OUTF(o, i) = sm[L.cvel + 6 * D.body_frame[i / 6] + i % 6];
+  TSYNC();
 }
+
 // ------------------------------------------------------------------------------------------ mj_fwdActuation
 __device__ __forceinline__ float muscleFL(float Ln, float lmin, float lmax) {
   if (Ln < lmin || Ln > lmax) return 0.f;
@@ -807,23 +840,17 @@ __device__ __noinline__ void muscleGainBias(float len, float vel, const float* l
   else if (Ln <= b) { const float x = (Ln - 1.f) / fmaxf(MINVAL, b - 1.f); *bias = -force * fpmax * 0.5f * x * x; }
   else { const float x = (Ln - b) / fmaxf(MINVAL, b - 1.f); *bias = -force * fpmax * (0.5f + x); }
 }
-__device__ __noinline__ void actuation(int slot, int fslot, SP sm, World W) {
+__device__ __noinline__ void actuation(int slot, int fslot, SP sm, Tm t, World W) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L; const FieldPtrs& F = tP[fslot].F;
   const int nu = D.nu, nv = D.nv;
   const bool on = !(D.disableflags & DSBL_ACTUATION);
   void* olen = F.p[MYO_F_ACTUATOR_LENGTH]; void* ovel = F.p[MYO_F_ACTUATOR_VELOCITY]; void* ofrc = F.p[MYO_F_ACTUATOR_FORCE];
   void* odot = F.p[MYO_F_ACT_DOT];
-  // #pragma unroll 1
-  for (int t = 0; t < D.nten; t++) sm[L.tforce + t] = 0.f;
-  // #pragma unroll 1
-  for (int i = 0; i < nv; i++) sm[L.qfrc_act + i] = 0.f;
-  // #pragma unroll 1
-  for (int i = 0; i < nu; i++) {
+  TFOR(i, nu) {
     const int id = D.act_trnid[i];
     const float gear = D.act_gear[i];
-    const bool ten = D.act_trntype[i] == 3;
     float len, vel;
-    if (ten) { len = gear * sm[L.tenlen + id]; vel = gear * sm[L.tenvel + id]; }
+    if (D.act_trntype[i] == 3) { len = gear * sm[L.tenlen + id]; vel = gear * sm[L.tenvel + id]; }
     else { len = gear * sm[L.qpos + D.jnt_qposadr[id]]; vel = gear * sm[L.qvel + D.jnt_dofadr[id]]; }
     float force = 0.f, adot = 0.f;
     const int aa = D.act_actadr[i];
@@ -863,39 +890,40 @@ __device__ __noinline__ void actuation(int slot, int fslot, SP sm, World W) {
     }
     sm[L.actforce + i] = force;
     if (aa >= 0) { sm[L.actdot + aa] = adot; if (odot) OUTF(odot, aa) = adot; }
-    if (ten) sm[L.tforce + id] += gear * force; else sm[L.qfrc_act + D.jnt_dofadr[id]] += gear * force;
     if (olen) OUTF(olen, i) = len;
     if (ovel) OUTF(ovel, i) = vel;
     if (ofrc) OUTF(ofrc, i) = force;
   }
-  // qfrc_actuator = moment^T force through the sparse tendon rows
-  // #pragma unroll 1
-  for (int t = 0; t < D.nten; t++) {
-    const float tf = sm[L.tforce + t];
-    if (tf == 0.f) continue;
-    // #pragma unroll 1
-    for (int n = D.ten_nzstart[t]; n < D.ten_nzstart[t + 1]; n++) sm[L.qfrc_act + D.nz_dof[n]] = fmaf(sm[L.tenJ + n], tf, sm[L.qfrc_act + D.nz_dof[n]]);
+  TSYNC();
+  TFOR(k, D.nten) {
+    float acc = 0.f;
+    for (int q = D.tact_start[k]; q < D.tact_start[k + 1]; q++) { const int a = D.tact_list[q]; acc += D.act_gear[a] * sm[L.actforce + a]; }
+    sm[L.tforce + k] = acc;
   }
-  // #pragma unroll 1
-  for (int i = 0; i < nv; i++) {
-    const float sf = sm[L.passive + i] - sm[L.bias + i] + sm[L.qfrc_act + i];
+  TSYNC();
+  // qfrc_actuator = moment^T force through the sparse tendon rows (column view), deterministic gathers
+  TFOR(i, nv) {
+    float acc = 0.f;
+    for (int c = D.col_start[i]; c < D.col_start[i + 1]; c++) { const int n = D.col_nz[c]; acc = fmaf(sm[L.tenJ + n], sm[L.tforce + D.nz_tendon[n]], acc); }
+    for (int q = D.dact_start[i]; q < D.dact_start[i + 1]; q++) { const int a = D.dact_list[q]; acc += D.act_gear[a] * sm[L.actforce + a]; }
+    sm[L.qfrc_act + i] = acc;
+    const float sf = sm[L.passive + i] - sm[L.bias + i] + acc;
     sm[L.smooth + i] = sf; sm[L.qacc_smooth + i] = sf;
   }
-  solveLDL(slot, sm + L.qLD, sm + L.qLDinv, sm + L.qacc_smooth);
+  TSYNC();
+  solveLDL(slot, sm + L.qLD, sm + L.qLDinv, sm + L.qacc_smooth, t);
   void* o;
-  if ((o = F.p[MYO_F_QFRC_ACTUATOR])) for (int i = 0; i < nv; i++) OUTF(o, i) = sm[L.qfrc_act + i];
-  if ((o = F.p[MYO_F_QFRC_SMOOTH])) for (int i = 0; i < nv; i++) OUTF(o, i) = sm[L.smooth + i];
-  if ((o = F.p[MYO_F_QACC_SMOOTH])) for (int i = 0; i < nv; i++) OUTF(o, i) = sm[L.qacc_smooth + i];
+  if ((o = F.p[MYO_F_QFRC_ACTUATOR])) TFOR(i, nv) OUTF(o, i) = sm[L.qfrc_act + i];
+  if ((o = F.p[MYO_F_QFRC_SMOOTH])) TFOR(i, nv) OUTF(o, i) = sm[L.smooth + i];
+  if ((o = F.p[MYO_F_QACC_SMOOTH])) TFOR(i, nv) OUTF(o, i) = sm[L.qacc_smooth + i];
   if ((o = F.p[MYO_F_ACTUATOR_MOMENT])) {
-    // #pragma unroll 1
-    for (int a = 0; a < nu; a++) {   // dense row = the tendon's sparse row scaled by the gear
+    TFOR(a, nu) {   // dense row = the tendon's sparse row scaled by the gear
       const int id = D.act_trnid[a];
       const bool ten = D.act_trntype[a] == 3;
       int k = ten ? D.ten_nzstart[id] : 0;
       const int kend = ten ? D.ten_nzstart[id + 1] : 0;
       const int jd = ten ? -1 : D.jnt_dofadr[id];
       const float gear = D.act_gear[a];
-      // #pragma unroll 1
       for (int i = 0; i < nv; i++) {
         float v = 0.f;
         if (k < kend && D.nz_dof[k] == i) { v = gear * sm[L.tenJ + k]; k++; }
@@ -905,6 +933,7 @@ __device__ __noinline__ void actuation(int slot, int fslot, SP sm, World W) {
     }
   }
 }
+
 // ------------------------------------------------------------------------------------------ collision
 // The convex narrow phase (Minkowski portal refinement on B - A) runs in float64: its result is defined by an
 // iteration with a 1e-6 stopping rule, and in float32 the portal degenerates near convergence (contact points of
@@ -1071,47 +1100,55 @@ __device__ __forceinline__ void makeFrame(f3 n, f3* y, f3* z) {
   *y = t; *z = cross(n, t);
 }
 // returns the number of contacts; contact record: dist, pos[3], normal[3], pair, efc_address, dim, spare[2]
-// Pass 1 (uniform over the warp): bounding-sphere / plane-distance filter over the static candidate-pair list, each
-// lane compacting ITS survivors.  Pass 2: lane-private survivor lists are walked in lock-step, so the narrow phase
-// runs max-over-lanes(#survivors) times instead of once per static pair; pair order (hence contact order) is kept.
-__device__ __noinline__ int collision(int slot, SP sm, int* status) {
+// Pass 1: bounding-sphere / plane-distance filter over the static candidate-pair list, TEAM pairs at a time, survivors
+// compacted in pair order by a team prefix sum.  Pass 2: narrow phase over the survivors, TEAM at a time, hits
+// compacted in the same order -- so contact order (hence geom1/geom2/efc_address) is MuJoCo's.
+__device__ __noinline__ int collision(int slot, SP sm, Tm t, int* status) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
   if (D.npair == 0) return 0;
-  // #pragma unroll 1
-  for (int c = 0; c < D.ncg; c++) {
+  TFOR(c, D.ncg) {
     const int f = D.cg_frame[c];
     auto o = sm + L.cgpose + 12 * c;
     st3(o, ld3(FR_POS(sm, L, f)) + mulM(FR_MAT(sm, L, f), ld3(D.cg_lpos + 3 * c)));
-    mulMM(o + 3, FR_MAT(sm, L, f), D.cg_lmat + 9 * c);
+    float M[9]; mulMM(M, FR_MAT(sm, L, f), D.cg_lmat + 9 * c);
+#pragma unroll
+    for (int k = 0; k < 9; k++) o[3 + k] = M[k];
   }
+  TSYNC();
   SPI cand = asInt(sm + L.cand);
   int ncand = 0;
-  // #pragma unroll 1
-  for (int pr = 0; pr < D.npair; pr++) {
-    const int c1 = D.pair_cg1[pr], c2 = D.pair_cg2[pr];
-    auto P1 = sm + L.cgpose + 12 * c1; auto P2 = sm + L.cgpose + 12 * c2;
-    const f3 d = ld3(P2) - ld3(P1);
-    const float margin = D.pair_prm[16 * pr];
-    bool pass;
-    if (D.cg_type[c1] == G_PLANE) pass = !(d.x * P1[5] + d.y * P1[8] + d.z * P1[11] > D.cg_rbound[c2] + margin);
-    else { const float r = D.cg_rbound[c1] + D.cg_rbound[c2] + margin; pass = !(dot(d, d) > r * r); }
-    if (pass) cand[ncand++] = pr;
+  for (int base = 0; base < D.npair; base += TEAM) {
+    const int pr = base + t.tl;
+    bool pass = false;
+    if (pr < D.npair) {
+      const int c1 = D.pair_cg1[pr], c2 = D.pair_cg2[pr];
+      auto P1 = sm + L.cgpose + 12 * c1; auto P2 = sm + L.cgpose + 12 * c2;
+      const f3 d = ld3(P2) - ld3(P1);
+      const float margin = D.pair_prm[16 * pr];
+      if (D.cg_type[c1] == G_PLANE) pass = !(d.x * P1[5] + d.y * P1[8] + d.z * P1[11] > D.cg_rbound[c2] + margin);
+      else { const float r = D.cg_rbound[c1] + D.cg_rbound[c2] + margin; pass = !(dot(d, d) > r * r); }
+    }
+    int total; const int at = ncand + teamExclScan(t, pass ? 1 : 0, &total);
+    if (pass) cand[at] = pr;
+    ncand += total;
   }
+  TSYNC();
   int ncon = 0;
-  // #pragma unroll 1
-  for (int k = 0; k < ncand; k++) {
-    const int pr = cand[k];
-    Hit h[2];
-    const int n = collidePair(slot, sm, pr, h);
-    // #pragma unroll 1
-    for (int q = 0; q < n; q++, ncon++) {
-      if (ncon >= D.nconmax) continue;
-      auto c = sm + L.con + 12 * ncon;
+  for (int base = 0; base < ncand; base += TEAM) {
+    const int k = base + t.tl;
+    Hit h[2]; int n = 0, pr = 0;
+    if (k < ncand) { pr = cand[k]; n = collidePair(slot, sm, pr, h); }
+    int total; int at = ncon + teamExclScan(t, n, &total);
+    for (int q = 0; q < n; q++, at++) {
+      if (at >= D.nconmax) continue;
+      auto c = sm + L.con + 12 * at;
       c[0] = h[q].dist; st3(c + 1, h[q].pos); st3(c + 4, h[q].nrm);
       c[7] = __int_as_float(pr); c[8] = __int_as_float(-1); c[9] = __int_as_float(D.pair_dim[pr]);
     }
+    ncon += total;
   }
   if (ncon > D.nconmax) { *status |= MYO_WORLD_NCON_OVERFLOW; ncon = D.nconmax; }
+  TSYNC();
   return ncon;
 }
 
@@ -1147,16 +1184,16 @@ __device__ __noinline__ void setRow(int slot, SP sm, int r, int type, int id, fl
   EFC(E_POS, r) = pos; EFC(E_MARGIN, r) = margin; EFC(E_FORCE, r) = 0.f;
 }
 // base-row products  out[b] = conJ[b] . x   for the nb*ncon contact base rows
-__device__ __noinline__ void baseMul(int slot, SP sm, int ncon, SP x, SP out) {
+__device__ __noinline__ void baseMul(int slot, SP sm, Tm t, int ncon, SP x, SP out) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
   const int nbr = D.maxbase * ncon, nv = D.nv;
-  // #pragma unroll 1
-  for (int b = 0; b < nbr; b++) {
+  TFOR(b, nbr) {
     auto J = sm + L.conJ + b * nv;
-    float acc = 0.f;
-    #pragma unroll 4
-    for (int k = 0; k < nv; k++) acc = fmaf(J[k], x[k], acc);
-    out[b] = acc;
+    float a0 = 0.f, a1 = 0.f;
+    int k = 0;
+    for (; k + 1 < nv; k += 2) { a0 = fmaf(J[k], x[k], a0); a1 = fmaf(J[k + 1], x[k + 1], a1); }
+    if (k < nv) a0 = fmaf(J[k], x[k], a0);
+    out[b] = a0 + a1;
   }
 }
 // J_r . x for one efc row (bx = base products of x)
@@ -1165,23 +1202,21 @@ __device__ __forceinline__ float rowMul(int slot, SP sm, int r, SP x, SP bx) {
   const int d0 = EFCI(E_DESC0, r), type = d0 & 3, id = d0 >> 2;
   const float coef = EFC(E_COEF, r);
   if (type == ROW_LIMJ) return coef * x[D.limj_dof[id]];
-  if (type == ROW_CON) { const int t = EFCI(E_DESC1, r); return bx[id] + (t >= 0 ? coef * bx[t] : 0.f); }
+  if (type == ROW_CON) { const int q = EFCI(E_DESC1, r); return bx[id] + (q >= 0 ? coef * bx[q] : 0.f); }
   if (type == ROW_EQ) { const int d2 = D.eq_dof2[id]; return x[D.eq_dof1[id]] + (d2 >= 0 ? coef * x[d2] : 0.f); }
-  const int t = D.limt_ten[id];
+  const int tn = D.limt_ten[id];
   float acc = 0.f;
-  // #pragma unroll 1
-  for (int n = D.ten_nzstart[t]; n < D.ten_nzstart[t + 1]; n++) acc += sm[L.tenJ + n] * x[D.nz_dof[n]];
+  for (int n = D.ten_nzstart[tn]; n < D.ten_nzstart[tn + 1]; n++) acc += sm[L.tenJ + n] * x[D.nz_dof[n]];
   return coef * acc;
 }
 
-__device__ __noinline__ int makeConstraint(int slot, SP sm, int ncon, int* status) {
+__device__ __noinline__ int makeConstraint(int slot, SP sm, Tm t, int ncon, int* status) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
   const int nv = D.nv, njmax = D.njmax;
   auto qpos = sm + L.qpos; auto qvel = sm + L.qvel;
   if (D.disableflags & DSBL_CONSTRAINT) return 0;
   // ---- equality rows (always active)
-  // #pragma unroll 1
-  for (int e = 0; e < D.neq; e++) {
+  TFOR(e, D.neq) {
     const int d1 = D.eq_dof1[e], d2 = D.eq_dof2[e], q1 = D.eq_q1[e], q2 = D.eq_q2[e];
     auto dt = D.eq_data + 5 * e;
     float pos, dpoly = 0.f, vel = qvel[d1];
@@ -1194,196 +1229,220 @@ __device__ __noinline__ int makeConstraint(int slot, SP sm, int ncon, int* statu
     setRow(slot, sm, e, ROW_EQ, e, -dpoly, 0, pos, 0.f, D.eq_prm[8 * e + 7], D.eq_prm + 8 * e, vel, 0.f);
   }
   int nefc = D.neq;
-  // ---- joint limits, then tendon limits
+  // ---- joint limits, then tendon limits (row order by a team prefix sum)
   const int nlim = D.nlimj + D.nlimt;
-  // #pragma unroll 1
-  for (int li = 0; li < nlim; li++) {
+  for (int base = 0; base < nlim; base += TEAM) {
+    const int li = base + t.tl;
+    float dlo = 1.f, dhi = 1.f, margin = 0.f; int cnt = 0;
     const bool isj = li < D.nlimj;
-    auto prm = isj ? D.limj_prm + 12 * li : D.limt_prm + 12 * (li - D.nlimj);
-    const float val = isj ? qpos[D.limj_q[li]] : sm[L.tenlen + D.limt_ten[li - D.nlimj]];
-    const float margin = prm[2], dlo = val - prm[0], dhi = prm[1] - val;
-    int r0 = -1, r1 = -1;
-    if (dlo < margin || dhi < margin) {
-      const float v = isj ? qvel[D.limj_dof[li]] : sm[L.tenvel + D.limt_ten[li - D.nlimj]];
-      const int id = isj ? li : li - D.nlimj, type = isj ? ROW_LIMJ : ROW_LIMT;
-      if (dlo < margin) { if (nefc < njmax) { r0 = nefc; setRow(slot, sm, nefc, type, id, 1.f, 0, dlo, margin, prm[10], prm + 3, v, 0.f); } nefc++; }
-      if (dhi < margin) { if (nefc < njmax) { r1 = nefc; setRow(slot, sm, nefc, type, id, -1.f, 0, dhi, margin, prm[10], prm + 3, -v, 0.f); } nefc++; }
+    const float* prm = nullptr;
+    if (li < nlim) {
+      prm = isj ? D.limj_prm + 12 * li : D.limt_prm + 12 * (li - D.nlimj);
+      const float val = isj ? qpos[D.limj_q[li]] : sm[L.tenlen + D.limt_ten[li - D.nlimj]];
+      margin = prm[2]; dlo = val - prm[0]; dhi = prm[1] - val;
+      cnt = (dlo < margin) + (dhi < margin);
     }
-    sm[L.limrow + 2 * li] = __int_as_float(r0); sm[L.limrow + 2 * li + 1] = __int_as_float(r1);
-  }
-  // ---- contacts: base Jacobian rows, then the pyramid rows
-  const int nb = D.maxbase;
-  auto bx = sm + L.basev;
-  // #pragma unroll 1
-  for (int c = 0; c < ncon; c++) {
-    auto cr = sm + L.con + 12 * c;
-    const int pr = __float_as_int(cr[7]), dim = __float_as_int(cr[9]);
-    auto pp = D.pair_prm + 16 * pr;
-    const float inc = pp[0] - pp[1];
-    const int rows = cr[0] < inc ? (dim == 1 ? 1 : 2 * (dim - 1)) : 0;
-    const int adr = (rows > 0 && nefc + rows <= njmax) ? nefc : -1;
-    cr[8] = __int_as_float(adr);
-    nefc += rows;
-    const int c1 = D.pair_cg1[pr], c2 = D.pair_cg2[pr];
-    const int f1 = D.cg_frame[c1], f2 = D.cg_frame[c2];
-    const f3 pos = ld3(cr + 1), n = ld3(cr + 4);
-    f3 y, z; makeFrame(n, &y, &z);
-    const int m1a = D.fr_mask[2 * f1], m1b = D.fr_mask[2 * f1 + 1], m2a = D.fr_mask[2 * f2], m2b = D.fr_mask[2 * f2 + 1];
-    auto J = sm + L.conJ + (c * nb) * nv;
-    float vn = 0.f, vy = 0.f, vz = 0.f, vr = 0.f;
-    // #pragma unroll 1
-    for (int k = 0; k < nv; k++) {
-      const int in1 = ((k < 32 ? m1a : m1b) >> (k & 31)) & 1, in2 = ((k < 32 ? m2a : m2b) >> (k & 31)) & 1;
-      f3 jp = mk3(0.f, 0.f, 0.f), jr = jp;
-      if (in1 != in2) {
-        const float s = (float)(in2 - in1);
-        auto cd = sm + L.cdof + 6 * k;
-        jr = ld3(cd) * s;
-        jp = (ld3(cd + 3) + cross(ld3(cd), pos - ld3(sm + L.rootcom + 3 * D.fr_root[D.dof_frame[k]]))) * s;
+    int total; int at = nefc + teamExclScan(t, cnt, &total);
+    if (li < nlim) {
+      int r0 = -1, r1 = -1;
+      if (cnt) {
+        const float v = isj ? qvel[D.limj_dof[li]] : sm[L.tenvel + D.limt_ten[li - D.nlimj]];
+        const int id = isj ? li : li - D.nlimj, type = isj ? ROW_LIMJ : ROW_LIMT;
+        if (dlo < margin) { if (at < njmax) { r0 = at; setRow(slot, sm, at, type, id, 1.f, 0, dlo, margin, prm[10], prm + 3, v, 0.f); } at++; }
+        if (dhi < margin) { if (at < njmax) { r1 = at; setRow(slot, sm, at, type, id, -1.f, 0, dhi, margin, prm[10], prm + 3, -v, 0.f); } at++; }
       }
-      const float qv = qvel[k];
-      const float jn = dot(n, jp);
-      J[k] = jn; vn = fmaf(jn, qv, vn);
-      if (nb > 1) { const float jy = dot(y, jp), jz = dot(z, jp); J[nv + k] = jy; J[2 * nv + k] = jz; vy = fmaf(jy, qv, vy); vz = fmaf(jz, qv, vz); }
-      if (nb > 3) { const float jt = dot(n, jr); J[3 * nv + k] = jt; vr = fmaf(jt, qv, vr); }
+      sm[L.limrow + 2 * li] = __int_as_float(r0); sm[L.limrow + 2 * li + 1] = __int_as_float(r1);
     }
-    const int bn = c * nb;
-    bx[bn] = vn; if (nb > 1) { bx[bn + 1] = vy; bx[bn + 2] = vz; } if (nb > 3) bx[bn + 3] = vr;
-    if (adr < 0) continue;
-    const float margin = inc, dist = cr[0];
-    const float tran = D.cg_invweight[2 * c1] + D.cg_invweight[2 * c2];
-    const float kb[7] = {pp[14], pp[15], pp[9], pp[10], pp[11], pp[12], pp[13]};
-    if (dim == 1) setRow(slot, sm, adr, ROW_CON, bn, 0.f, -1, dist, margin, tran, kb, bx[bn], 0.f);
-    else {
-      const float mu0 = pp[2] * rsqrtf(D.impratio);
-      const float dA0 = tran + pp[2] * pp[2] * tran;   // first pyramid row sets the shared regulariser
-      // #pragma unroll 1
-      for (int k = 1; k < dim; k++) {
-        const float mu = pp[1 + k];
-        const int bt = bn + k;
-        setRow(slot, sm, adr + 2 * (k - 1), ROW_CON, bn, mu, bt, dist, margin, dA0, kb, bx[bn] + mu * bx[bt], 2.f * mu0 * mu0);
-        setRow(slot, sm, adr + 2 * (k - 1) + 1, ROW_CON, bn, -mu, bt, dist, margin, dA0, kb, bx[bn] - mu * bx[bt], 2.f * mu0 * mu0);
+    nefc += total;
+  }
+  // ---- contacts: row addresses, base Jacobian rows, pyramid rows
+  if (ncon > 0) {
+    const int nb = D.maxbase;
+    for (int base = 0; base < ncon; base += TEAM) {
+      const int c = base + t.tl;
+      int rows = 0;
+      if (c < ncon) {
+        auto cr = sm + L.con + 12 * c;
+        const int pr = __float_as_int(cr[7]), dim = __float_as_int(cr[9]);
+        const float inc = D.pair_prm[16 * pr] - D.pair_prm[16 * pr + 1];
+        if (cr[0] < inc) rows = dim == 1 ? 1 : 2 * (dim - 1);
+      }
+      int total; const int at = nefc + teamExclScan(t, rows, &total);
+      if (c < ncon) sm[L.con + 12 * c + 8] = __int_as_float((rows > 0 && at + rows <= njmax) ? at : -1);
+      nefc += total;
+    }
+    // base Jacobian rows: one item = (contact, dof)
+    TFOR(idx, ncon * nv) {
+      const int c = idx / nv, k = idx - c * nv;
+      auto cr = sm + L.con + 12 * c;
+      const int pr = __float_as_int(cr[7]);
+      const int f1 = D.cg_frame[D.pair_cg1[pr]], f2 = D.cg_frame[D.pair_cg2[pr]];
+      const int in1 = (D.fr_mask[2 * f1 + (k >> 5)] >> (k & 31)) & 1, in2 = (D.fr_mask[2 * f2 + (k >> 5)] >> (k & 31)) & 1;
+      auto J = sm + L.conJ + (c * nb) * nv + k;
+      if (in1 == in2) { J[0] = 0.f; if (nb > 1) { J[nv] = 0.f; J[2 * nv] = 0.f; } if (nb > 3) J[3 * nv] = 0.f; continue; }
+      const f3 pos = ld3(cr + 1), n = ld3(cr + 4);
+      f3 y, z; makeFrame(n, &y, &z);
+      const float sgn = (float)(in2 - in1);
+      auto cd = sm + L.cdof + 6 * k;
+      const f3 jr = ld3(cd) * sgn;
+      const f3 jp = (ld3(cd + 3) + cross(ld3(cd), pos - ld3(sm + L.rootcom + 3 * D.fr_root[D.dof_frame[k]]))) * sgn;
+      J[0] = dot(n, jp);
+      if (nb > 1) { J[nv] = dot(y, jp); J[2 * nv] = dot(z, jp); }
+      if (nb > 3) J[3 * nv] = dot(n, jr);
+    }
+    TSYNC();
+    auto bx = sm + L.basev;
+    baseMul(slot, sm, t, ncon, qvel, bx);
+    TSYNC();
+    TFOR(c, ncon) {
+      auto cr = sm + L.con + 12 * c;
+      const int adr = __float_as_int(cr[8]);
+      if (adr < 0) continue;
+      const int pr = __float_as_int(cr[7]), dim = __float_as_int(cr[9]);
+      auto pp = D.pair_prm + 16 * pr;
+      const float margin = pp[0] - pp[1], dist = cr[0];
+      const int c1 = D.pair_cg1[pr], c2 = D.pair_cg2[pr];
+      const float tran = D.cg_invweight[2 * c1] + D.cg_invweight[2 * c2];
+      const float kb[7] = {pp[14], pp[15], pp[9], pp[10], pp[11], pp[12], pp[13]};
+      const int bn = c * nb;
+      if (dim == 1) setRow(slot, sm, adr, ROW_CON, bn, 0.f, -1, dist, margin, tran, kb, bx[bn], 0.f);
+      else {
+        const float mu0 = pp[2] * rsqrtf(D.impratio);
+        const float dA0 = tran + pp[2] * pp[2] * tran;   // first pyramid row sets the shared regulariser
+        for (int k = 1; k < dim; k++) {
+          const float mu = pp[1 + k];
+          const int bt = bn + k;
+          setRow(slot, sm, adr + 2 * (k - 1), ROW_CON, bn, mu, bt, dist, margin, dA0, kb, bx[bn] + mu * bx[bt], 2.f * mu0 * mu0);
+          setRow(slot, sm, adr + 2 * (k - 1) + 1, ROW_CON, bn, -mu, bt, dist, margin, dA0, kb, bx[bn] - mu * bx[bt], 2.f * mu0 * mu0);
+        }
       }
     }
   }
   if (nefc > njmax) { *status |= MYO_WORLD_NEFC_OVERFLOW; nefc = njmax; }
+  TSYNC();
   return nefc;
 }
 
 // ------------------------------------------------------------------------------------------ Newton solver (mj_fwdConstraint)
-__device__ __noinline__ void mulMsparse(int slot, SP qM, SP x, SP out) {
+__device__ __noinline__ void mulMsparse(int slot, SP qM, SP x, SP out, Tm t) {
   const DevModel& D = tP[slot].D;
-  const int nv = D.nv;
-  // #pragma unroll 1
-  for (int i = 0; i < nv; i++) out[i] = 0.f;
-  // #pragma unroll 1
-  for (int i = 0; i < nv; i++) {
+  TFOR(i, D.nv) {
     const int a = D.dof_Madr[i], d = D.dof_rowlen[i];
-    const float xi = x[i];
-    float acc = qM[a] * xi;
-    // #pragma unroll 1
-    for (int s = 1; s < d; s++) { const int j = D.M_col[a + s]; const float m = qM[a + s]; acc = fmaf(m, x[j], acc); out[j] = fmaf(m, xi, out[j]); }
-    out[i] += acc;
+    float acc = 0.f;
+    for (int q = 0; q < d; q++) acc = fmaf(qM[a + q], x[D.M_col[a + q]], acc);
+    for (int e = D.desc_start[i]; e < D.desc_start[i + 1]; e++) acc = fmaf(qM[D.desc_idx[e]], x[D.desc_dof[e]], acc);
+    out[i] = acc;
   }
 }
 __device__ __forceinline__ bool rowOn(int d0, float jar) { return ((d0 & 3) == ROW_EQ) || jar < 0.f; }
-// jar = J x - aref for all rows, returns the constraint cost; force/active are implied by jar
-__device__ __noinline__ float residualCost(int slot, SP sm, int ncon, int nefc, SP x) {
+// jar = J x - aref for all rows, returns the (team-uniform) constraint cost; force/active are implied by jar
+__device__ __noinline__ float residualCost(int slot, SP sm, Tm t, int ncon, int nefc, SP x) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
   auto bx = sm + L.basev;
-  baseMul(slot, sm, ncon, x, bx);
+  baseMul(slot, sm, t, ncon, x, bx);
+  TSYNC();
   float cost = 0.f;
-  // #pragma unroll 1
-  for (int r = 0; r < nefc; r++) {
+  TFOR(r, nefc) {
     const float jar = rowMul(slot, sm, r, x, bx) - EFC(E_AREF, r);
     EFC(E_JAR, r) = jar;
     if (rowOn(EFCI(E_DESC0, r), jar)) cost = fmaf(0.5f * EFC(E_D, r) * jar, jar, cost);
   }
-  return cost;
+  TSYNC();
+  return teamSum(t, cost);
 }
-// forces from jar, then out = J^T f
-__device__ __noinline__ void constraintForce(int slot, SP sm, int ncon, int nefc, SP out) {
+// forces from jar, then out = J^T f  (deterministic gathers, no atomics)
+__device__ __noinline__ void constraintForce(int slot, SP sm, Tm t, int ncon, int nefc, SP out) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
   const int nv = D.nv, nb = D.maxbase;
-  // #pragma unroll 1
-  for (int k = 0; k < nv; k++) out[k] = 0.f;
-  // #pragma unroll 1
-  for (int r = 0; r < nefc; r++) {
-    const int d0 = EFCI(E_DESC0, r), type = d0 & 3, id = d0 >> 2;
-    const float jar = EFC(E_JAR, r);
-    const float f = rowOn(d0, jar) ? -EFC(E_D, r) * jar : 0.f;
-    EFC(E_FORCE, r) = f;
-    if (f == 0.f || type == ROW_CON) continue;
-    const float coef = EFC(E_COEF, r);
-    if (type == ROW_LIMJ) out[D.limj_dof[id]] += coef * f;
-    else if (type == ROW_EQ) { out[D.eq_dof1[id]] += f; const int d2 = D.eq_dof2[id]; if (d2 >= 0) out[d2] += coef * f; }
-    else {
-      const int t = D.limt_ten[id];
-      // #pragma unroll 1
-      for (int n = D.ten_nzstart[t]; n < D.ten_nzstart[t + 1]; n++) out[D.nz_dof[n]] += coef * f * sm[L.tenJ + n];
-    }
-  }
-  // #pragma unroll 1
-  for (int c = 0; c < ncon; c++) {
+  TFOR(r, nefc) { const float jar = EFC(E_JAR, r); EFC(E_FORCE, r) = rowOn(EFCI(E_DESC0, r), jar) ? -EFC(E_D, r) * jar : 0.f; }
+  TSYNC();
+  auto bf = sm + L.basev + nb * D.nconmax;
+  TFOR(b, nb * ncon) {
+    const int c = b / nb, k = b - c * nb;
     auto cr = sm + L.con + 12 * c;
     const int adr = __float_as_int(cr[8]), dim = __float_as_int(cr[9]);
-    if (adr < 0) continue;
-    float bf[4] = {0.f, 0.f, 0.f, 0.f};
-    if (dim == 1) bf[0] = EFC(E_FORCE, adr);
-    else
-      // #pragma unroll 1
-      for (int k = 1; k < dim; k++) {
-        const float fp = EFC(E_FORCE, adr + 2 * (k - 1)), fm = EFC(E_FORCE, adr + 2 * (k - 1) + 1);
-        bf[0] += fp + fm; bf[k] = EFC(E_COEF, adr + 2 * (k - 1)) * (fp - fm);
-      }
-    if (bf[0] == 0.f && bf[1] == 0.f && bf[2] == 0.f && bf[3] == 0.f) continue;
-    auto J = sm + L.conJ + (c * nb) * nv;
-    // #pragma unroll 1
-    for (int k = 0; k < nv; k++) {
-      float acc = fmaf(J[k], bf[0], out[k]);
-      if (dim > 1) { acc = fmaf(J[nv + k], bf[1], acc); acc = fmaf(J[2 * nv + k], bf[2], acc); }
-      if (dim > 3) acc = fmaf(J[3 * nv + k], bf[3], acc);
-      out[k] = acc;
+    float f = 0.f;
+    if (adr >= 0 && k < dim) {
+      if (dim == 1) f = EFC(E_FORCE, adr);
+      else if (k == 0) { for (int p = 0; p < 2 * (dim - 1); p++) f += EFC(E_FORCE, adr + p); }
+      else f = EFC(E_COEF, adr + 2 * (k - 1)) * (EFC(E_FORCE, adr + 2 * (k - 1)) - EFC(E_FORCE, adr + 2 * (k - 1) + 1));
     }
+    bf[b] = f;
   }
+  TSYNC();
+  TFOR(k, nv) {
+    float acc = 0.f;
+    for (int e = D.dofeq_start[k]; e < D.dofeq_start[k + 1]; e++) {
+      const int v = D.dofeq_list[e], r = v >> 1;
+      acc += (v & 1) ? EFC(E_COEF, r) * EFC(E_FORCE, r) : EFC(E_FORCE, r);
+    }
+    const int li = D.dof_limidx[k];
+    if (li >= 0)
+      for (int q = 0; q < 2; q++) { const int r = __float_as_int(sm[L.limrow + 2 * li + q]); if (r >= 0) acc += EFC(E_COEF, r) * EFC(E_FORCE, r); }
+    if (D.nlimt > 0)
+      for (int c = D.col_start[k]; c < D.col_start[k + 1]; c++) {
+        const int n = D.col_nz[c], lt = D.ten_limidx[D.nz_tendon[n]];
+        if (lt < 0) continue;
+        for (int q = 0; q < 2; q++) {
+          const int r = __float_as_int(sm[L.limrow + 2 * (D.nlimj + lt) + q]);
+          if (r >= 0) acc += EFC(E_COEF, r) * EFC(E_FORCE, r) * sm[L.tenJ + n];
+        }
+      }
+    float a1 = 0.f;
+    int b = 0;
+    for (; b + 1 < nb * ncon; b += 2) { acc = fmaf(sm[L.conJ + b * nv + k], bf[b], acc); a1 = fmaf(sm[L.conJ + (b + 1) * nv + k], bf[b + 1], a1); }
+    if (b < nb * ncon) acc = fmaf(sm[L.conJ + b * nv + k], bf[b], acc);
+    out[k] = acc + a1;
+  }
+  TSYNC();
 }
 // H = M + J^T D_active J (lower triangle), Cholesky in place
-__device__ __noinline__ void hessianFactor(int slot, SP sm, int ncon, int nefc) {
+__device__ __noinline__ void hessianFactor(int slot, SP sm, Tm t, int ncon, int nefc) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
   const int nv = D.nv, nb = D.maxbase;
   auto H = sm + L.H;
-  // #pragma unroll 1
-  for (int i = 0; i < nv * nv; i++) H[i] = 0.f;
-  // #pragma unroll 1
-  for (int e = 0; e < D.nM; e++) H[D.M_row[e] * nv + D.M_col[e]] = sm[L.qM + e];
-  // #pragma unroll 1
-  for (int r = 0; r < nefc; r++) {
-    const int d0 = EFCI(E_DESC0, r), type = d0 & 3, id = d0 >> 2;
-    if (type == ROW_CON || !rowOn(d0, EFC(E_JAR, r))) continue;
-    const float Dr = EFC(E_D, r), coef = EFC(E_COEF, r);
-    if (type == ROW_LIMJ) { const int k = D.limj_dof[id]; H[k * nv + k] += Dr; }
-    else if (type == ROW_EQ) {
-      const int d1 = D.eq_dof1[id], d2 = D.eq_dof2[id];
-      H[d1 * nv + d1] += Dr;
-      if (d2 >= 0) { H[max(d1, d2) * nv + min(d1, d2)] += Dr * coef; H[d2 * nv + d2] += Dr * coef * coef; }
-    } else {
-      const int t = D.limt_ten[id], n0 = D.ten_nzstart[t], n1 = D.ten_nzstart[t + 1];
-      // #pragma unroll 1
-      for (int a = n0; a < n1; a++)
-        // #pragma unroll 1
-        for (int b = n0; b <= a; b++) H[D.nz_dof[a] * nv + D.nz_dof[b]] += Dr * sm[L.tenJ + a] * sm[L.tenJ + b];   // nz sorted by dof
+  TFOR(i, nv * nv) H[i] = 0.f;
+  TSYNC();
+  TFOR(e, D.nM) H[D.M_row[e] * nv + D.M_col[e]] = sm[L.qM + e];
+  TSYNC();
+  TFOR(k, nv) {
+    const int li = D.dof_limidx[k];
+    if (li < 0) continue;
+    for (int q = 0; q < 2; q++) {
+      const int r = __float_as_int(sm[L.limrow + 2 * li + q]);
+      if (r >= 0 && EFC(E_JAR, r) < 0.f) H[k * nv + k] += EFC(E_D, r);
     }
   }
-  // #pragma unroll 1
+  TSYNC();
+  if (t.tl == 0)
+    for (int e = 0; e < D.neq; e++) {
+      const int d1 = D.eq_dof1[e], d2 = D.eq_dof2[e];
+      const float Dr = EFC(E_D, e), c = EFC(E_COEF, e);
+      H[d1 * nv + d1] += Dr;
+      if (d2 >= 0) { H[max(d1, d2) * nv + min(d1, d2)] += Dr * c; H[d2 * nv + d2] += Dr * c * c; }
+    }
+  for (int lt = 0; lt < D.nlimt; lt++)
+    for (int q = 0; q < 2; q++) {
+      const int r = __float_as_int(sm[L.limrow + 2 * (D.nlimj + lt) + q]);
+      if (r < 0 || !(EFC(E_JAR, r) < 0.f)) continue;
+      TSYNC();
+      const int tn = D.limt_ten[lt], n0 = D.ten_nzstart[tn], cnt = D.ten_nzstart[tn + 1] - n0;
+      const float Dr = EFC(E_D, r);
+      TFOR(i, cnt * cnt) {
+        const int a = i / cnt, b = i - a * cnt;
+        const int da = D.nz_dof[n0 + a], db = D.nz_dof[n0 + b];
+        if (da >= db) H[da * nv + db] += Dr * sm[L.tenJ + n0 + a] * sm[L.tenJ + n0 + b];
+      }
+    }
+  TSYNC();
   for (int c = 0; c < ncon; c++) {
     auto cr = sm + L.con + 12 * c;
     const int adr = __float_as_int(cr[8]), dim = __float_as_int(cr[9]);
     if (adr < 0) continue;
     // weights in base-row space: W = sum_p D_p w_p w_p^T, w_p = e_n +- mu e_t
     float Wnn = 0.f, Wnt[3] = {0.f, 0.f, 0.f}, Wtt[3] = {0.f, 0.f, 0.f};
-    if (dim == 1) { if (rowOn(EFCI(E_DESC0, adr), EFC(E_JAR, adr))) Wnn = EFC(E_D, adr); }
+    if (dim == 1) { if (EFC(E_JAR, adr) < 0.f) Wnn = EFC(E_D, adr); }
     else
-      // #pragma unroll 1
       for (int k = 1; k < dim; k++) {
         const int r0 = adr + 2 * (k - 1);
         const float mu = EFC(E_COEF, r0);
@@ -1392,20 +1451,16 @@ __device__ __noinline__ void hessianFactor(int slot, SP sm, int ncon, int nefc) 
       }
     if (Wnn == 0.f) continue;
     auto Jn = sm + L.conJ + (c * nb) * nv;
-    // #pragma unroll 1
-    for (int r = 0; r < nv; r++) {
-      // u_r = W-weighted combination for row r:  H[r, c] += sum_k u_k[r] * J_k[c]
+    TFOR(r, nv) {   // each lane owns whole rows of H: no write conflicts, no sync between contacts
       const float jn = Jn[r];
       float un = Wnn * jn, ut[3] = {0.f, 0.f, 0.f};
       bool any = jn != 0.f;
-      // #pragma unroll 1
       for (int k = 1; k < dim; k++) {
         const float jt = Jn[k * nv + r];
         un = fmaf(Wnt[k - 1], jt, un); ut[k - 1] = fmaf(Wnt[k - 1], jn, Wtt[k - 1] * jt);
         any |= jt != 0.f;
       }
       if (!any) continue;
-      // #pragma unroll 1
       for (int cc = 0; cc <= r; cc++) {
         float acc = fmaf(un, Jn[cc], H[r * nv + cc]);
         for (int k = 1; k < dim; k++) acc = fmaf(ut[k - 1], Jn[k * nv + cc], acc);
@@ -1413,58 +1468,58 @@ __device__ __noinline__ void hessianFactor(int slot, SP sm, int ncon, int nefc) 
       }
     }
   }
-  // Cholesky (row-oriented, lower triangle in place)
-  // #pragma unroll 1
+  TSYNC();
+  // left-looking Cholesky, lanes over rows
   for (int j = 0; j < nv; j++) {
-    auto Hj = H + j * nv;
-    // #pragma unroll 1
-    for (int k = 0; k < j; k++) {
-      auto Hk = H + k * nv;
-      float s = Hj[k];
-      // #pragma unroll 1
-      for (int q = 0; q < k; q++) s = fmaf(-Hj[q], Hk[q], s);
-      Hj[k] = s / Hk[k];
+    float sj = 0.f;
+    for (int r = j + t.tl; r < nv; r += TEAM) {
+      float s0 = H[r * nv + j], s1 = 0.f;
+      int k = 0;
+      for (; k + 1 < j; k += 2) { s0 = fmaf(-H[r * nv + k], H[j * nv + k], s0); s1 = fmaf(-H[r * nv + k + 1], H[j * nv + k + 1], s1); }
+      if (k < j) s0 = fmaf(-H[r * nv + k], H[j * nv + k], s0);
+      s0 += s1;
+      if (r == j) sj = s0; else H[r * nv + j] = s0;
     }
-    float s = Hj[j];
-    // #pragma unroll 1
-    for (int q = 0; q < j; q++) s = fmaf(-Hj[q], Hj[q], s);
-    Hj[j] = sqrtf(fmaxf(s, MINVAL));
+    sj = teamBcast(t, sj, 0);
+    const float d = sqrtf(fmaxf(sj, MINVAL)), inv = 1.f / d;
+    for (int r = j + t.tl; r < nv; r += TEAM) { if (r == j) H[j * nv + j] = d; else H[r * nv + j] *= inv; }
+    TSYNC();
   }
 }
-__device__ __noinline__ void cholSolve(int slot, SP H, SP x) {
+__device__ __noinline__ void cholSolve(int slot, SP H, SP x, Tm t) {
   const int nv = tP[slot].D.nv;
-  // #pragma unroll 1
   for (int j = 0; j < nv; j++) {
-    float s = x[j];
-    // #pragma unroll 1
-    for (int k = 0; k < j; k++) s = fmaf(-H[j * nv + k], x[k], s);
-    x[j] = s / H[j * nv + j];
+    const float xj = x[j] / H[j * nv + j];
+    TSYNC();
+    if (t.tl == 0) x[j] = xj;
+    for (int r = j + 1 + t.tl; r < nv; r += TEAM) x[r] = fmaf(-H[r * nv + j], xj, x[r]);
+    TSYNC();
   }
-  // #pragma unroll 1
   for (int j = nv - 1; j >= 0; j--) {
     const float xj = x[j] / H[j * nv + j];
-    x[j] = xj;
-    // #pragma unroll 1
-    for (int r = 0; r < j; r++) x[r] = fmaf(-H[j * nv + r], xj, x[r]);
+    TSYNC();
+    if (t.tl == 0) x[j] = xj;
+    for (int r = t.tl; r < j; r += TEAM) x[r] = fmaf(-H[j * nv + r], xj, x[r]);
+    TSYNC();
   }
 }
 struct LsPt { float alpha, cost, d0, d1; };
-__device__ __noinline__ LsPt lsEval(int slot, SP sm, int nefc, float a, const float* qg) {
+__device__ __noinline__ LsPt lsEval(int slot, SP sm, Tm t, int nefc, float a, const float* qg) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
-  float q0 = qg[0], q1 = qg[1], q2 = qg[2];
-  // #pragma unroll 1
-  for (int r = 0; r < nefc; r++) {
+  float q0 = 0.f, q1 = 0.f, q2 = 0.f;
+  TFOR(r, nefc) {
     const float jar = EFC(E_JAR, r), jv = EFC(E_JV, r), x = fmaf(a, jv, jar);
     if (rowOn(EFCI(E_DESC0, r), x)) {
       const float Dr = EFC(E_D, r);
       q0 = fmaf(0.5f * Dr * jar, jar, q0); q1 = fmaf(Dr * jar, jv, q1); q2 = fmaf(0.5f * Dr * jv, jv, q2);
     }
   }
+  q0 = teamSum(t, q0) + qg[0]; q1 = teamSum(t, q1) + qg[1]; q2 = teamSum(t, q2) + qg[2];
   LsPt p; p.alpha = a; p.cost = a * a * q2 + a * q1 + q0; p.d0 = 2.f * a * q2 + q1; p.d1 = 2.f * q2;
   if (p.d1 <= 0.f) p.d1 = MINVAL;
   return p;
 }
-__device__ __noinline__ int solveNewton(int slot, SP sm, int ncon, int nefc, int* status) {
+__device__ __noinline__ int solveNewton(int slot, SP sm, Tm t, int ncon, int nefc, int* status) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
   const int nv = D.nv;
   auto qacc = sm + L.qacc; auto Ma = sm + L.nvec; auto grad = Ma + nv; auto search = grad + nv; auto Mv = search + nv;
@@ -1474,53 +1529,54 @@ __device__ __noinline__ int solveNewton(int slot, SP sm, int ncon, int nefc, int
   // warm start: cheaper of qacc_warmstart and qacc_smooth
   float costW = 3.4e38f;
   if (!(D.disableflags & DSBL_WARMSTART)) {
-    mulMsparse(slot, sm + L.qM, sm + L.warm, Ma);
+    mulMsparse(slot, sm + L.qM, sm + L.warm, Ma, t);
+    TSYNC();
     float g = 0.f;
-    // #pragma unroll 1
-    for (int k = 0; k < nv; k++) g = fmaf(0.5f * (Ma[k] - smooth[k]), sm[L.warm + k] - qas[k], g);
-    costW = g + residualCost(slot, sm, ncon, nefc, sm + L.warm);
+    TFOR(k, nv) g = fmaf(0.5f * (Ma[k] - smooth[k]), sm[L.warm + k] - qas[k], g);
+    costW = teamSum(t, g) + residualCost(slot, sm, t, ncon, nefc, sm + L.warm);
   }
-  const float costS = residualCost(slot, sm, ncon, nefc, qas);
+  const float costS = residualCost(slot, sm, t, ncon, nefc, qas);
   const bool useWarm = !(costW > costS);
-  // #pragma unroll 1
-  for (int k = 0; k < nv; k++) qacc[k] = useWarm ? sm[L.warm + k] : qas[k];
-  mulMsparse(slot, sm + L.qM, qacc, Ma);
+  TFOR(k, nv) qacc[k] = useWarm ? sm[L.warm + k] : qas[k];
+  TSYNC();
+  mulMsparse(slot, sm + L.qM, qacc, Ma, t);
+  TSYNC();
   float gauss = 0.f;
-  // #pragma unroll 1
-  for (int k = 0; k < nv; k++) gauss = fmaf(0.5f * (Ma[k] - smooth[k]), qacc[k] - qas[k], gauss);
-  float cost = gauss + residualCost(slot, sm, ncon, nefc, qacc);
+  TFOR(k, nv) gauss = fmaf(0.5f * (Ma[k] - smooth[k]), qacc[k] - qas[k], gauss);
+  gauss = teamSum(t, gauss);
+  float cost = gauss + residualCost(slot, sm, t, ncon, nefc, qacc);
   int iter = 0;
   // #pragma unroll 1
   for (;;) {
     // gradient and termination tests
-    constraintForce(slot, sm, ncon, nefc, tmp);
+    constraintForce(slot, sm, t, ncon, nefc, tmp);
     float gn = 0.f;
-    // #pragma unroll 1
-    for (int k = 0; k < nv; k++) { const float g = Ma[k] - smooth[k] - tmp[k]; grad[k] = g; search[k] = g; gn = fmaf(g, g, gn); }
-    gn = sqrtf(gn);
+    TFOR(k, nv) { const float g = Ma[k] - smooth[k] - tmp[k]; grad[k] = g; search[k] = g; gn = fmaf(g, g, gn); }
+    gn = sqrtf(teamSum(t, gn));
+    TSYNC();
     if (iter > 0 && scale * gn < D.tolerance) break;
     if (iter >= D.iterations) { *status |= MYO_WORLD_SOLVER_MAXITER; break; }
-    hessianFactor(slot, sm, ncon, nefc);
-    cholSolve(slot, sm + L.H, search);
+    hessianFactor(slot, sm, t, ncon, nefc);
+    cholSolve(slot, sm + L.H, search, t);
     float sn = 0.f;
-    // #pragma unroll 1
-    for (int k = 0; k < nv; k++) { const float s = -search[k]; search[k] = s; sn = fmaf(s, s, sn); }
-    sn = sqrtf(sn);
+    TFOR(k, nv) { const float s = -search[k]; search[k] = s; sn = fmaf(s, s, sn); }
+    sn = sqrtf(teamSum(t, sn));
+    TSYNC();
     if (sn < MINVAL) break;
     // exact line search along `search`
-    mulMsparse(slot, sm + L.qM, search, Mv);
+    mulMsparse(slot, sm + L.qM, search, Mv, t);
     auto bx = sm + L.basev;
-    baseMul(slot, sm, ncon, search, bx);
-    // #pragma unroll 1
-    for (int r = 0; r < nefc; r++) EFC(E_JV, r) = rowMul(slot, sm, r, search, bx);
+    baseMul(slot, sm, t, ncon, search, bx);
+    TSYNC();
+    TFOR(r, nefc) EFC(E_JV, r) = rowMul(slot, sm, r, search, bx);
     float g1 = 0.f, g2 = 0.f;
-    // #pragma unroll 1
-    for (int k = 0; k < nv; k++) { g1 = fmaf(search[k], Ma[k] - smooth[k], g1); g2 = fmaf(0.5f * search[k], Mv[k], g2); }
-    const float qg[3] = {gauss, g1, g2};
+    TFOR(k, nv) { g1 = fmaf(search[k], Ma[k] - smooth[k], g1); g2 = fmaf(0.5f * search[k], Mv[k], g2); }
+    TSYNC();
+    const float qg[3] = {gauss, teamSum(t, g1), teamSum(t, g2)};
     const float gtol = D.tolerance * D.ls_tolerance * sn / scale;
     int lsiter = 0;
-    LsPt p0 = lsEval(slot, sm, nefc, 0.f, qg); lsiter++;
-    LsPt p1 = lsEval(slot, sm, nefc, p0.alpha - p0.d0 / p0.d1, qg); lsiter++;
+    LsPt p0 = lsEval(slot, sm, t, nefc, 0.f, qg); lsiter++;
+    LsPt p1 = lsEval(slot, sm, t, nefc, p0.alpha - p0.d0 / p0.d1, qg); lsiter++;
     if (p0.cost < p1.cost) p1 = p0;
     bool done = fabsf(p1.d0) < gtol;
     if (!done) {
@@ -1529,7 +1585,7 @@ __device__ __noinline__ int solveNewton(int slot, SP sm, int ncon, int nefc, int
       // #pragma unroll 1
       while (p1.d0 * dir <= -gtol && lsiter < D.ls_iterations) {
         p2 = p1; have2 = true;
-        p1 = lsEval(slot, sm, nefc, p1.alpha - p1.d0 / p1.d1, qg); lsiter++;
+        p1 = lsEval(slot, sm, t, nefc, p1.alpha - p1.d0 / p1.d1, qg); lsiter++;
         if (fabsf(p1.d0) < gtol) { done = true; break; }
       }
       if (!done && lsiter < D.ls_iterations && have2) {
@@ -1541,7 +1597,7 @@ __device__ __noinline__ int solveNewton(int slot, SP sm, int ncon, int nefc, int
           const float ca[3] = {lo.alpha - lo.d0 / lo.d1, hi.alpha - hi.d0 / hi.d1, 0.5f * (lo.alpha + hi.alpha)};
           LsPt cand[3];
           // #pragma unroll 1
-          for (int q = 0; q < 3; q++) { cand[q] = lsEval(slot, sm, nefc, ca[q], qg); lsiter++; }
+          for (int q = 0; q < 3; q++) { cand[q] = lsEval(slot, sm, t, nefc, ca[q], qg); lsiter++; }
           // #pragma unroll 1
           for (int q = 0; q < 3; q++) {
             if (done) break;
@@ -1560,44 +1616,43 @@ __device__ __noinline__ int solveNewton(int slot, SP sm, int ncon, int nefc, int
     }
     const float alpha = p1.alpha;
     if (alpha == 0.f) break;
-    // #pragma unroll 1
-    for (int k = 0; k < nv; k++) { qacc[k] = fmaf(alpha, search[k], qacc[k]); Ma[k] = fmaf(alpha, Mv[k], Ma[k]); }
+    TFOR(k, nv) { qacc[k] = fmaf(alpha, search[k], qacc[k]); Ma[k] = fmaf(alpha, Mv[k], Ma[k]); }
     float c2 = 0.f;
-    // #pragma unroll 1
-    for (int r = 0; r < nefc; r++) {
+    TFOR(r, nefc) {
       const float jar = fmaf(alpha, EFC(E_JV, r), EFC(E_JAR, r));
       EFC(E_JAR, r) = jar;
       if (rowOn(EFCI(E_DESC0, r), jar)) c2 = fmaf(0.5f * EFC(E_D, r) * jar, jar, c2);
     }
+    TSYNC();
     float g = 0.f;
-    // #pragma unroll 1
-    for (int k = 0; k < nv; k++) g = fmaf(0.5f * (Ma[k] - smooth[k]), qacc[k] - qas[k], g);
-    gauss = g;
-    const float newcost = gauss + c2;
+    TFOR(k, nv) g = fmaf(0.5f * (Ma[k] - smooth[k]), qacc[k] - qas[k], g);
+    gauss = teamSum(t, g);
+    const float newcost = gauss + teamSum(t, c2);
     iter++;
     const float improvement = scale * (cost - newcost);
     cost = newcost;
     if (improvement < D.tolerance) break;
   }
-  constraintForce(slot, sm, ncon, nefc, sm + L.qfrc_con);
+  constraintForce(slot, sm, t, ncon, nefc, sm + L.qfrc_con);
   return iter;
 }
 
 // ------------------------------------------------------------------------------------------ contact / efc outputs
-__device__ __noinline__ void writeConstraintOutputs(int slot, int fslot, SP sm, World W, int ncon, int nefc, int niter) {
+__device__ __noinline__ void writeConstraintOutputs(int slot, int fslot, SP sm, Tm t, World W, int ncon, int nefc, int niter) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L; const FieldPtrs& F = tP[fslot].F;
   const int nv = D.nv, ncm = D.nconmax, njm = D.njmax;
   void* p;
-  if ((p = F.p[MYO_F_NCON])) OUTI(p, 0) = ncon;
-  if ((p = F.p[MYO_F_NEFC])) OUTI(p, 0) = nefc;
-  if ((p = F.p[MYO_F_SOLVER_NITER])) OUTI(p, 0) = niter;
+  if (t.tl == 0) {
+    if ((p = F.p[MYO_F_NCON])) OUTI(p, 0) = ncon;
+    if ((p = F.p[MYO_F_NEFC])) OUTI(p, 0) = nefc;
+    if ((p = F.p[MYO_F_SOLVER_NITER])) OUTI(p, 0) = niter;
+  }
   void* cg = F.p[MYO_F_CONTACT_GEOM]; void* cdim = F.p[MYO_F_CONTACT_DIM]; void* cadr = F.p[MYO_F_CONTACT_EFC_ADDRESS];
   void* cdist = F.p[MYO_F_CONTACT_DIST]; void* cpos = F.p[MYO_F_CONTACT_POS]; void* cfr = F.p[MYO_F_CONTACT_FRAME];
   void* cinc = F.p[MYO_F_CONTACT_INCLUDEMARGIN]; void* cfri = F.p[MYO_F_CONTACT_FRICTION]; void* csr = F.p[MYO_F_CONTACT_SOLREF];
   void* csi = F.p[MYO_F_CONTACT_SOLIMP];
   if (cg || cdim || cadr || cdist || cpos || cfr || cinc || cfri || csr || csi) {
-    // #pragma unroll 1
-    for (int c = 0; c < ncm; c++) {
+    TFOR(c, ncm) {
       const bool on = c < ncon;
       auto cr = sm + L.con + 12 * c;
       const int pr = on ? __float_as_int(cr[7]) : 0;
@@ -1622,8 +1677,7 @@ __device__ __noinline__ void writeConstraintOutputs(int slot, int fslot, SP sm, 
   void* epos = F.p[MYO_F_EFC_POS]; void* emar = F.p[MYO_F_EFC_MARGIN]; void* eD = F.p[MYO_F_EFC_D]; void* earef = F.p[MYO_F_EFC_AREF];
   void* efrc = F.p[MYO_F_EFC_FORCE]; void* etyp = F.p[MYO_F_EFC_TYPE]; void* eJ = F.p[MYO_F_EFC_J];
   if (epos || emar || eD || earef || efrc || etyp || eJ) {
-    // #pragma unroll 1
-    for (int r = 0; r < njm; r++) {
+    TFOR(r, njm) {
       const bool on = r < nefc;
       if (epos) OUTF(epos, r) = on ? EFC(E_POS, r) : 0.f;
       if (emar) OUTF(emar, r) = on ? EFC(E_MARGIN, r) : 0.f;
@@ -1635,14 +1689,13 @@ __device__ __noinline__ void writeConstraintOutputs(int slot, int fslot, SP sm, 
       if (eJ) {
         const float coef = on ? EFC(E_COEF, r) : 0.f;
         const int t1 = on && type == ROW_CON ? EFCI(E_DESC1, r) : -1;
-        // #pragma unroll 1
         for (int k = 0; k < nv; k++) {
           float v = 0.f;
           if (on) {
             if (type == ROW_LIMJ) v = D.limj_dof[id] == k ? coef : 0.f;
             else if (type == ROW_EQ) v = D.eq_dof1[id] == k ? 1.f : (D.eq_dof2[id] == k ? coef : 0.f);
             else if (type == ROW_CON) v = sm[L.conJ + id * nv + k] + (t1 >= 0 ? coef * sm[L.conJ + t1 * nv + k] : 0.f);
-            else { const int t = D.limt_ten[id]; for (int q = D.ten_nzstart[t]; q < D.ten_nzstart[t + 1]; q++) if (D.nz_dof[q] == k) v = coef * sm[L.tenJ + q]; }
+            else { const int tn = D.limt_ten[id]; for (int q = D.ten_nzstart[tn]; q < D.ten_nzstart[tn + 1]; q++) if (D.nz_dof[q] == k) v = coef * sm[L.tenJ + q]; }
           }
           OUTF(eJ, r * nv + k) = v;
         }
@@ -1651,39 +1704,40 @@ __device__ __noinline__ void writeConstraintOutputs(int slot, int fslot, SP sm, 
   }
 }
 
-__device__ __forceinline__ bool anyBad(SP v, int n) {
+__device__ __forceinline__ bool anyBad(SP v, int n, Tm t) {
   bool bad = false;
-  // #pragma unroll 1
-  for (int i = 0; i < n; i++) bad |= !(fabsf(v[i]) < 1e10f);
-  return bad;
+  TFOR(i, n) bad |= !(fabsf(v[i]) < 1e10f);
+  return teamAny(t, bad);
 }
-__device__ __noinline__ void resetState(int slot, SP sm) {
+__device__ __noinline__ void resetState(int slot, SP sm, Tm t) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
-  for (int i = 0; i < D.nq; i++) sm[L.qpos + i] = D.qpos0[i];
-  for (int i = 0; i < D.nv; i++) { sm[L.qvel + i] = 0.f; sm[L.warm + i] = 0.f; }
-  for (int i = 0; i < D.na; i++) sm[L.act + i] = 0.f;
+  TFOR(i, D.nq) sm[L.qpos + i] = D.qpos0[i];
+  TFOR(i, D.nv) { sm[L.qvel + i] = 0.f; sm[L.warm + i] = 0.f; }
+  TFOR(i, D.na) sm[L.act + i] = 0.f;
+  TSYNC();
 }
 
-// mj_forward for one world: everything from the state in `sm`; returns nefc
-__device__ __forceinline__ void forwardWorld(int slot, int fslot, SP sm, World W, bool last, int* status, int* ncon_o, int* nefc_o, int* niter_o) {
+// mj_forward for one world: everything from the state in the scratch
+__device__ __forceinline__ void forwardWorld(int slot, int fslot, SP sm, Tm t, World W, bool last, int* status, int* ncon_o, int* nefc_o, int* niter_o) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
   const int nv = D.nv;
-  kinematics(slot, sm);
-  comPos(slot, sm);
-  if (last) writePositionOutputs(slot, fslot, sm, W);
-  tendons(slot, fslot, sm, W);
-  inertia(slot, fslot, sm, W);
-  const int ncon = (D.disableflags & (DSBL_CONTACT | DSBL_CONSTRAINT)) ? 0 : collision(slot, sm, status);
-  velocity(slot, fslot, sm, W);
-  actuation(slot, fslot, sm, W);
-  const int nefc = makeConstraint(slot, sm, ncon, status);
+  kinematics(slot, sm, t);
+  comPos(slot, sm, t);
+  if (last) writePositionOutputs(slot, fslot, sm, t, W);
+  tendons(slot, fslot, sm, t, W);
+  inertia(slot, fslot, sm, t, W);
+  const int ncon = (D.disableflags & (DSBL_CONTACT | DSBL_CONSTRAINT)) ? 0 : collision(slot, sm, t, status);
+  velocity(slot, fslot, sm, t, W);
+  actuation(slot, fslot, sm, t, W);
+  const int nefc = makeConstraint(slot, sm, t, ncon, status);
   int niter = 0;
   if (nefc == 0) {
-    for (int i = 0; i < nv; i++) { const float a = sm[L.qacc_smooth + i]; sm[L.qacc + i] = a; sm[L.warm + i] = a; sm[L.qfrc_con + i] = 0.f; }
+    TFOR(i, nv) { const float a = sm[L.qacc_smooth + i]; sm[L.qacc + i] = a; sm[L.warm + i] = a; sm[L.qfrc_con + i] = 0.f; }
   } else {
-    niter = solveNewton(slot, sm, ncon, nefc, status);
-    for (int i = 0; i < nv; i++) sm[L.warm + i] = sm[L.qacc + i];
+    niter = solveNewton(slot, sm, t, ncon, nefc, status);
+    TFOR(i, nv) sm[L.warm + i] = sm[L.qacc + i];
   }
+  TSYNC();
   *ncon_o = ncon; *nefc_o = nefc; *niter_o = niter;
 }
 
@@ -1692,6 +1746,7 @@ __global__ void __launch_bounds__(32) stepKernel(int slot, int nworld, int nsub,
                                                  float* __restrict__ scratch) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L; const FieldPtrs& F = tP[slot].F;
   const int lane = threadIdx.x & 31, g = lane / TEAM;
+  Tm t; t.tl = lane % TEAM; t.mask = TEAM == 32 ? 0xffffffffu : (((1u << TEAM) - 1u) << (g * TEAM));
   World W; W.w = (size_t)blockIdx.x * SCR_STRIDE + g; W.nw = (size_t)nworld;
   if (W.w >= W.nw) return;
   SP sm; sm.p = scratch + (size_t)blockIdx.x * L.total * SCR_STRIDE + g;
@@ -1702,67 +1757,64 @@ __global__ void __launch_bounds__(32) stepKernel(int slot, int nworld, int nsub,
   int status = gs ? OUTI(gs, 0) : 0;
   float time = OUTF(gt, 0);
   if (do_reset) {
-    resetState(slot, sm);
-    for (int i = 0; i < nu; i++) sm[L.ctrl + i] = 0.f;
+    resetState(slot, sm, t);
+    TFOR(i, nu) sm[L.ctrl + i] = 0.f;
     time = 0.f; status = 0;
   } else {
-    for (int i = 0; i < nq; i++) sm[L.qpos + i] = OUTF(gq, i);
-    for (int i = 0; i < nv; i++) { sm[L.qvel + i] = OUTF(gv, i); sm[L.warm + i] = OUTF(gw, i); }
-    for (int i = 0; i < na; i++) sm[L.act + i] = OUTF(ga, i);
-    for (int i = 0; i < nu; i++) sm[L.ctrl + i] = OUTF(gc, i);
+    TFOR(i, nq) sm[L.qpos + i] = OUTF(gq, i);
+    TFOR(i, nv) { sm[L.qvel + i] = OUTF(gv, i); sm[L.warm + i] = OUTF(gw, i); }
+    TFOR(i, na) sm[L.act + i] = OUTF(ga, i);
+    TFOR(i, nu) sm[L.ctrl + i] = OUTF(gc, i);
   }
+  TSYNC();
   const int nloop = forward_only ? 1 : nsub;
-  // #pragma unroll 1
   for (int sub = 0; sub < nloop; sub++) {
     const bool last = sub == nloop - 1;
     const int fslot = last ? slot : MYO_NSLOT;
     if (!forward_only) {   // mj_checkPos / mj_checkVel
-      if (anyBad(sm + L.qpos, nq)) { resetState(slot, sm); status |= MYO_WORLD_BADQPOS; }
-      if (anyBad(sm + L.qvel, nv)) { resetState(slot, sm); status |= MYO_WORLD_BADQVEL; }
+      if (anyBad(sm + L.qpos, nq, t)) { TSYNC(); resetState(slot, sm, t); status |= MYO_WORLD_BADQPOS; }
+      if (anyBad(sm + L.qvel, nv, t)) { TSYNC(); resetState(slot, sm, t); status |= MYO_WORLD_BADQVEL; }
     }
     int ncon = 0, nefc = 0, niter = 0;
-    forwardWorld(slot, fslot, sm, W, last, &status, &ncon, &nefc, &niter);
-    if (!forward_only && anyBad(sm + L.qacc, nv)) {   // mj_checkAcc: reset the world and redo its forward pass
-      resetState(slot, sm);
+    forwardWorld(slot, fslot, sm, t, W, last, &status, &ncon, &nefc, &niter);
+    if (!forward_only && anyBad(sm + L.qacc, nv, t)) {   // mj_checkAcc: reset the world and redo its forward pass
+      TSYNC();
+      resetState(slot, sm, t);
       status |= MYO_WORLD_BADQACC;
-      forwardWorld(slot, fslot, sm, W, last, &status, &ncon, &nefc, &niter);
+      forwardWorld(slot, fslot, sm, t, W, last, &status, &ncon, &nefc, &niter);
     }
     if (last) {
-      writeConstraintOutputs(slot, fslot, sm, W, ncon, nefc, niter);
+      writeConstraintOutputs(slot, fslot, sm, t, W, ncon, nefc, niter);
       void* o;
-      if ((o = F.p[MYO_F_QACC])) for (int i = 0; i < nv; i++) OUTF(o, i) = sm[L.qacc + i];
-      if ((o = F.p[MYO_F_QFRC_CONSTRAINT])) for (int i = 0; i < nv; i++) OUTF(o, i) = sm[L.qfrc_con + i];
-      if ((o = F.p[MYO_F_QFRC_INVERSE])) for (int i = 0; i < nv; i++) OUTF(o, i) = 0.f;
+      if ((o = F.p[MYO_F_QACC])) TFOR(i, nv) OUTF(o, i) = sm[L.qacc + i];
+      if ((o = F.p[MYO_F_QFRC_CONSTRAINT])) TFOR(i, nv) OUTF(o, i) = sm[L.qfrc_con + i];
+      if ((o = F.p[MYO_F_QFRC_INVERSE])) TFOR(i, nv) OUTF(o, i) = 0.f;
     }
     if (forward_only) break;
     // ---- mj_Euler with implicit joint damping
     const float h = D.timestep;
     auto qa = sm + L.tmpv;
     if (D.any_damping) {
-      // #pragma unroll 1
-      for (int i = 0; i < nv; i++) {
-        const int a = D.dof_Madr[i], d = D.dof_rowlen[i];
-        sm[L.qH + a] = sm[L.qM + a] + h * D.dof_damping[i];
-        for (int s = 1; s < d; s++) sm[L.qH + a + s] = sm[L.qM + a + s];
-        qa[i] = sm[L.smooth + i] + sm[L.qfrc_con + i];
-      }
-      factorLDL(slot, sm + L.qH, sm + L.qHinv);
-      solveLDL(slot, sm + L.qH, sm + L.qHinv, qa);
+      TFOR(e, D.nM) sm[L.qH + e] = sm[L.qM + e] + (D.M_row[e] == D.M_col[e] ? h * D.dof_damping[D.M_row[e]] : 0.f);
+      TFOR(i, nv) qa[i] = sm[L.smooth + i] + sm[L.qfrc_con + i];
+      TSYNC();
+      factorLDL(slot, sm + L.qH, sm + L.qHinv, t);
+      solveLDL(slot, sm + L.qH, sm + L.qHinv, qa, t);
     } else {
-      for (int i = 0; i < nv; i++) qa[i] = sm[L.qacc + i];
+      TFOR(i, nv) qa[i] = sm[L.qacc + i];
+      TSYNC();
     }
     if (!(D.disableflags & DSBL_ACTUATION))
-      // #pragma unroll 1
-      for (int i = 0; i < nu; i++) {
+      TFOR(i, nu) {
         const int aa = D.act_actadr[i];
         if (aa < 0) continue;
         float a = fmaf(h, sm[L.actdot + aa], sm[L.act + aa]);
         if (D.act_flags[i] & ACT_ACTLIMITED) a = clipf(a, D.act_actrange[2 * i], D.act_actrange[2 * i + 1]);
         sm[L.act + aa] = a;
       }
-    for (int i = 0; i < nv; i++) sm[L.qvel + i] = fmaf(h, qa[i], sm[L.qvel + i]);
-    // #pragma unroll 1
-    for (int j = 0; j < D.njnt; j++) {
+    TFOR(i, nv) sm[L.qvel + i] = fmaf(h, qa[i], sm[L.qvel + i]);
+    TSYNC();
+    TFOR(j, D.njnt) {
       const int qa_ = D.jnt_qposadr[j], da = D.jnt_dofadr[j];
       if (D.jnt_type[j] == JNT_FREE) {
         for (int k = 0; k < 3; k++) sm[L.qpos + qa_ + k] = fmaf(h, sm[L.qvel + da + k], sm[L.qpos + qa_ + k]);
@@ -1777,16 +1829,17 @@ __global__ void __launch_bounds__(32) stepKernel(int slot, int nworld, int nsub,
       } else sm[L.qpos + qa_] = fmaf(h, sm[L.qvel + da], sm[L.qpos + qa_]);
     }
     time += h;
+    TSYNC();
   }
   // ---- state out
   if (!forward_only || do_reset) {
-    for (int i = 0; i < nq; i++) OUTF(gq, i) = sm[L.qpos + i];
-    for (int i = 0; i < nv; i++) OUTF(gv, i) = sm[L.qvel + i];
-    for (int i = 0; i < na; i++) OUTF(ga, i) = sm[L.act + i];
-    OUTF(gt, 0) = time;
+    TFOR(i, nq) OUTF(gq, i) = sm[L.qpos + i];
+    TFOR(i, nv) OUTF(gv, i) = sm[L.qvel + i];
+    TFOR(i, na) OUTF(ga, i) = sm[L.act + i];
+    if (t.tl == 0) OUTF(gt, 0) = time;
   }
-  for (int i = 0; i < nv; i++) OUTF(gw, i) = sm[L.warm + i];
-  if (gs) OUTI(gs, 0) = status;
+  TFOR(i, nv) OUTF(gw, i) = sm[L.warm + i];
+  if (gs && t.tl == 0) OUTI(gs, 0) = status;
 }
 
 // known-answer hook for the rotation helpers above (tests/: reference KATs of myosuite/utils/quat_math.py)
@@ -1801,35 +1854,33 @@ __global__ void quatKatKernel(int n, const float* __restrict__ qa, const float* 
   st3(rotated + 3 * i, mulM(R, mk3(b.x, b.y, b.z)));
 }
 
-int64_t g_tpw_launches = 0;
 
 }  // namespace
 
-int64_t myo_tpw_launch_counter() { return g_tpw_launches; }
-int myo_tpw_param_slots() { return MYO_NSLOT; }
+#define CAT2_(a, b) a##b
+#define CAT2(a, b) CAT2_(a, b)
+#define VFN(name) CAT2(name, TEAM)
 
-int myo_tpw_upload_params(int slot, const DevModel& D, const SmemLayout& L, const FieldPtrs& F, void* stream) {
+int VFN(myo_team_upload_)(int slot, const DevModel& D, const SmemLayout& L, const FieldPtrs& F, void* stream) {
   static TParams staging[MYO_NSLOT];   // must outlive the async copy
   if (slot < 0 || slot >= MYO_NSLOT) return -1;
   TParams& P = staging[slot];
   P.D = D; P.L = L; P.F = F;
   return cudaMemcpyToSymbolAsync(tP, &P, sizeof(TParams), (size_t)slot * sizeof(TParams), cudaMemcpyHostToDevice, (cudaStream_t)stream) == cudaSuccess ? 0 : -1;
 }
-
-int myo_tpw_launch_step(int slot, const SmemLayout& L, int nworld, int nsub, int forward_only, const int* reset_mask, int do_reset,
-                        float* scratch, void* stream) {
+int VFN(myo_team_launch_)(int slot, const SmemLayout& L, int nworld, int nsub, int forward_only, const int* reset_mask, int do_reset,
+                          float* scratch, void* stream) {
   const int nwarp = (nworld + SCR_STRIDE - 1) / SCR_STRIDE;
   stepKernel<<<nwarp, 32, 0, (cudaStream_t)stream>>>(slot, nworld, nsub, forward_only, reset_mask, do_reset, scratch);
-  g_tpw_launches++;
   return cudaPeekAtLastError() == cudaSuccess ? 0 : -1;
 }
 // floats of scratch a batch of nworld worlds needs
-size_t myo_tpw_scratch_floats(const SmemLayout& L, int nworld) {
+size_t VFN(myo_team_scratch_)(const SmemLayout& L, int nworld) {
   return (size_t)((nworld + SCR_STRIDE - 1) / SCR_STRIDE) * L.total * SCR_STRIDE;
 }
-
-int myo_tpw_launch_quat_kat(int n, const float* qa, const float* qb, float* prod, float* mat, float* rotated, void* stream) {
+#if TEAM == 1
+int myo_launch_quat_kat(int n, const float* qa, const float* qb, float* prod, float* mat, float* rotated, void* stream) {
   quatKatKernel<<<(n + 127) / 128, 128, 0, (cudaStream_t)stream>>>(n, qa, qb, prod, mat, rotated);
-  g_tpw_launches++;
   return cudaPeekAtLastError() == cudaSuccess ? 0 : -1;
 }
+#endif

@@ -1,2 +1,1 @@
-for w in 32 16 8 4 2; do echo "wpw $w"; MYO_WPW=$w tools/sweep.sh 8192; done
-echo "auto"; tools/sweep.sh 8192 32768 65536
+for t in 1 2 4 8 16; do echo "== team $t"; MYO_TEAM=$t timeout 300 python tools/dev_parity.py hand legs 2>&1 | grep -E "bad|match|drift|FAILED" | cut -c1-200; MYO_TEAM=$t tools/sweep.sh 8192; done
