@@ -145,7 +145,7 @@ struct Tm { int tl; unsigned mask; };
 #else
 #define TSYNC() __syncwarp(t.mask)
 #endif
-#define TFOR(i, n) for (int i = t.tl; i < (n); i += TEAM)
+#define TFOR(i, n) _Pragma("unroll 1") for (int i = t.tl; i < (n); i += TEAM)
 __device__ __forceinline__ float teamSum(Tm t, float v) {
 #pragma unroll
   for (int o = TEAM / 2; o > 0; o >>= 1) v += __shfl_xor_sync(t.mask, v, o);
@@ -1717,73 +1717,101 @@ __device__ __noinline__ void resetState(int slot, SP sm, Tm t) {
   TSYNC();
 }
 
+// The warps of a CTA walk the phases of the step together (a CTA barrier between phases): the step is several
+// hundred KB of SASS, far beyond the instruction caches, and keeping an SM's warps inside the same few KB of code
+// removes most instruction-fetch stalls.  Teams still diverge freely inside a phase (contacts, solver iterations).
+#define PHASE_SYNC() __syncthreads()
 // mj_forward for one world: everything from the state in the scratch
-__device__ __forceinline__ void forwardWorld(int slot, int fslot, SP sm, Tm t, World W, bool last, int* status, int* ncon_o, int* nefc_o, int* niter_o) {
+__device__ __forceinline__ void forwardWorld(int slot, int fslot, SP sm, Tm t, World W, bool live, bool last, int* status, int* ncon_o, int* nefc_o, int* niter_o) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
   const int nv = D.nv;
-  kinematics(slot, sm, t);
-  comPos(slot, sm, t);
-  if (last) writePositionOutputs(slot, fslot, sm, t, W);
-  tendons(slot, fslot, sm, t, W);
-  inertia(slot, fslot, sm, t, W);
-  const int ncon = (D.disableflags & (DSBL_CONTACT | DSBL_CONSTRAINT)) ? 0 : collision(slot, sm, t, status);
-  velocity(slot, fslot, sm, t, W);
-  actuation(slot, fslot, sm, t, W);
-  const int nefc = makeConstraint(slot, sm, t, ncon, status);
-  int niter = 0;
-  if (nefc == 0) {
-    TFOR(i, nv) { const float a = sm[L.qacc_smooth + i]; sm[L.qacc + i] = a; sm[L.warm + i] = a; sm[L.qfrc_con + i] = 0.f; }
-  } else {
-    niter = solveNewton(slot, sm, t, ncon, nefc, status);
-    TFOR(i, nv) sm[L.warm + i] = sm[L.qacc + i];
+  if (live) { kinematics(slot, sm, t); comPos(slot, sm, t); }
+  PHASE_SYNC();
+  if (live && last) writePositionOutputs(slot, fslot, sm, t, W);
+  PHASE_SYNC();
+  if (live) tendons(slot, fslot, sm, t, W);
+  PHASE_SYNC();
+  if (live) inertia(slot, fslot, sm, t, W);
+  PHASE_SYNC();
+  int ncon = 0, nefc = 0, niter = 0;
+  if (live && !(D.disableflags & (DSBL_CONTACT | DSBL_CONSTRAINT))) ncon = collision(slot, sm, t, status);
+  PHASE_SYNC();
+  if (live) velocity(slot, fslot, sm, t, W);
+  PHASE_SYNC();
+  if (live) actuation(slot, fslot, sm, t, W);
+  PHASE_SYNC();
+  if (live) nefc = makeConstraint(slot, sm, t, ncon, status);
+  PHASE_SYNC();
+  if (live) {
+    if (nefc == 0) {
+      TFOR(i, nv) { const float a = sm[L.qacc_smooth + i]; sm[L.qacc + i] = a; sm[L.warm + i] = a; sm[L.qfrc_con + i] = 0.f; }
+    } else {
+      niter = solveNewton(slot, sm, t, ncon, nefc, status);
+      TFOR(i, nv) sm[L.warm + i] = sm[L.qacc + i];
+    }
+    TSYNC();
   }
-  TSYNC();
+  PHASE_SYNC();
   *ncon_o = ncon; *nefc_o = nefc; *niter_o = niter;
 }
 
-// One warp = SCR_STRIDE worlds, TEAM lanes each.  `scratch`: [nwarps][SmemLayout.total][SCR_STRIDE] floats.
-__global__ void __launch_bounds__(32) stepKernel(int slot, int nworld, int nsub, int forward_only, const int* __restrict__ mask, int do_reset,
-                                                 float* __restrict__ scratch) {
+// One warp = SCR_STRIDE worlds, TEAM lanes each; CTA_WARPS warps per CTA.  `scratch`: [nwarps][SmemLayout.total][SCR_STRIDE].
+#ifndef CTA_WARPS
+#define CTA_WARPS 8
+#endif
+#ifndef CTA_MINBLOCKS
+#define CTA_MINBLOCKS 2   // <= 128 registers: two 8-warp CTAs per SM, so 8192 worlds x 8 lanes are resident in one wave
+#endif
+__global__ void __launch_bounds__(32 * CTA_WARPS, CTA_MINBLOCKS) stepKernel(int slot, int nworld, int nsub, int forward_only, const int* __restrict__ mask,
+                                                             int do_reset, float* __restrict__ scratch) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L; const FieldPtrs& F = tP[slot].F;
   const int lane = threadIdx.x & 31, g = lane / TEAM;
+  const size_t warp = (size_t)blockIdx.x * CTA_WARPS + (threadIdx.x >> 5);
   Tm t; t.tl = lane % TEAM; t.mask = TEAM == 32 ? 0xffffffffu : (((1u << TEAM) - 1u) << (g * TEAM));
-  World W; W.w = (size_t)blockIdx.x * SCR_STRIDE + g; W.nw = (size_t)nworld;
-  if (W.w >= W.nw) return;
-  SP sm; sm.p = scratch + (size_t)blockIdx.x * L.total * SCR_STRIDE + g;
-  if (do_reset && mask && !mask[W.w]) return;
+  World W; W.w = warp * SCR_STRIDE + g; W.nw = (size_t)nworld;
+  const bool live = W.w < W.nw && !(do_reset && mask && !mask[W.w]);
+  if (!live) W.w = 0;
+  SP sm; sm.p = scratch + warp * L.total * SCR_STRIDE + g;
   const int nq = D.nq, nv = D.nv, na = D.na, nu = D.nu;
   void* gq = F.p[MYO_F_QPOS]; void* gv = F.p[MYO_F_QVEL]; void* ga = F.p[MYO_F_ACT]; void* gc = F.p[MYO_F_CTRL];
   void* gw = F.p[MYO_F_QACC_WARMSTART]; void* gt = F.p[MYO_F_TIME]; void* gs = F.p[MYO_F_STATUS];
-  int status = gs ? OUTI(gs, 0) : 0;
-  float time = OUTF(gt, 0);
-  if (do_reset) {
-    resetState(slot, sm, t);
-    TFOR(i, nu) sm[L.ctrl + i] = 0.f;
-    time = 0.f; status = 0;
-  } else {
-    TFOR(i, nq) sm[L.qpos + i] = OUTF(gq, i);
-    TFOR(i, nv) { sm[L.qvel + i] = OUTF(gv, i); sm[L.warm + i] = OUTF(gw, i); }
-    TFOR(i, na) sm[L.act + i] = OUTF(ga, i);
-    TFOR(i, nu) sm[L.ctrl + i] = OUTF(gc, i);
+  int status = 0;
+  float time = 0.f;
+  if (live) {
+    status = gs ? OUTI(gs, 0) : 0;
+    time = OUTF(gt, 0);
+    if (do_reset) {
+      resetState(slot, sm, t);
+      TFOR(i, nu) sm[L.ctrl + i] = 0.f;
+      time = 0.f; status = 0;
+    } else {
+      TFOR(i, nq) sm[L.qpos + i] = OUTF(gq, i);
+      TFOR(i, nv) { sm[L.qvel + i] = OUTF(gv, i); sm[L.warm + i] = OUTF(gw, i); }
+      TFOR(i, na) sm[L.act + i] = OUTF(ga, i);
+      TFOR(i, nu) sm[L.ctrl + i] = OUTF(gc, i);
+    }
+    TSYNC();
   }
-  TSYNC();
   const int nloop = forward_only ? 1 : nsub;
   for (int sub = 0; sub < nloop; sub++) {
     const bool last = sub == nloop - 1;
     const int fslot = last ? slot : MYO_NSLOT;
-    if (!forward_only) {   // mj_checkPos / mj_checkVel
+    if (live && !forward_only) {   // mj_checkPos / mj_checkVel
       if (anyBad(sm + L.qpos, nq, t)) { TSYNC(); resetState(slot, sm, t); status |= MYO_WORLD_BADQPOS; }
       if (anyBad(sm + L.qvel, nv, t)) { TSYNC(); resetState(slot, sm, t); status |= MYO_WORLD_BADQVEL; }
     }
     int ncon = 0, nefc = 0, niter = 0;
-    forwardWorld(slot, fslot, sm, t, W, last, &status, &ncon, &nefc, &niter);
-    if (!forward_only && anyBad(sm + L.qacc, nv, t)) {   // mj_checkAcc: reset the world and redo its forward pass
+    forwardWorld(slot, fslot, sm, t, W, live, last, &status, &ncon, &nefc, &niter);
+    // mj_checkAcc: a world whose qacc went bad is reset (qpos0, zero velocity / activation) and flagged; this substep
+    // does not integrate it, its next forward pass starts from the reset state.
+    bool skip = false;
+    if (live && !forward_only && anyBad(sm + L.qacc, nv, t)) {
       TSYNC();
       resetState(slot, sm, t);
       status |= MYO_WORLD_BADQACC;
-      forwardWorld(slot, fslot, sm, t, W, last, &status, &ncon, &nefc, &niter);
+      skip = true;
     }
-    if (last) {
+    if (live && last) {
       writeConstraintOutputs(slot, fslot, sm, t, W, ncon, nefc, niter);
       void* o;
       if ((o = F.p[MYO_F_QACC])) TFOR(i, nv) OUTF(o, i) = sm[L.qacc + i];
@@ -1791,6 +1819,7 @@ __global__ void __launch_bounds__(32) stepKernel(int slot, int nworld, int nsub,
       if ((o = F.p[MYO_F_QFRC_INVERSE])) TFOR(i, nv) OUTF(o, i) = 0.f;
     }
     if (forward_only) break;
+    if (live && !skip) {
     // ---- mj_Euler with implicit joint damping
     const float h = D.timestep;
     auto qa = sm + L.tmpv;
@@ -1830,8 +1859,11 @@ __global__ void __launch_bounds__(32) stepKernel(int slot, int nworld, int nsub,
     }
     time += h;
     TSYNC();
+    }
+    PHASE_SYNC();
   }
   // ---- state out
+  if (!live) return;
   if (!forward_only || do_reset) {
     TFOR(i, nq) OUTF(gq, i) = sm[L.qpos + i];
     TFOR(i, nv) OUTF(gv, i) = sm[L.qvel + i];
@@ -1871,12 +1903,13 @@ int VFN(myo_team_upload_)(int slot, const DevModel& D, const SmemLayout& L, cons
 int VFN(myo_team_launch_)(int slot, const SmemLayout& L, int nworld, int nsub, int forward_only, const int* reset_mask, int do_reset,
                           float* scratch, void* stream) {
   const int nwarp = (nworld + SCR_STRIDE - 1) / SCR_STRIDE;
-  stepKernel<<<nwarp, 32, 0, (cudaStream_t)stream>>>(slot, nworld, nsub, forward_only, reset_mask, do_reset, scratch);
+  stepKernel<<<(nwarp + CTA_WARPS - 1) / CTA_WARPS, 32 * CTA_WARPS, 0, (cudaStream_t)stream>>>(slot, nworld, nsub, forward_only, reset_mask, do_reset, scratch);
   return cudaPeekAtLastError() == cudaSuccess ? 0 : -1;
 }
 // floats of scratch a batch of nworld worlds needs
 size_t VFN(myo_team_scratch_)(const SmemLayout& L, int nworld) {
-  return (size_t)((nworld + SCR_STRIDE - 1) / SCR_STRIDE) * L.total * SCR_STRIDE;
+  const size_t nwarp = (size_t)(nworld + SCR_STRIDE - 1) / SCR_STRIDE;
+  return (nwarp + CTA_WARPS - 1) / CTA_WARPS * CTA_WARPS * L.total * SCR_STRIDE;
 }
 #if TEAM == 1
 int myo_launch_quat_kat(int n, const float* qa, const float* qb, float* prod, float* mat, float* rotated, void* stream) {
