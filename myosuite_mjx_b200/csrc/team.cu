@@ -24,6 +24,9 @@
 #include "internal.h"
 
 #define MINVAL 1e-15f
+#ifndef GRAD_NOISE
+#define GRAD_NOISE 2e-6f   // float32 noise floor of the Newton gradient relative to the magnitude of its terms
+#endif
 #ifndef TEAM
 #define TEAM 1   // lanes per world
 #endif
@@ -1550,11 +1553,16 @@ __device__ __noinline__ int solveNewton(int slot, SP sm, Tm t, int ncon, int nef
   for (;;) {
     // gradient and termination tests
     constraintForce(slot, sm, t, ncon, nefc, tmp);
-    float gn = 0.f;
-    TFOR(k, nv) { const float g = Ma[k] - smooth[k] - tmp[k]; grad[k] = g; search[k] = g; gn = fmaf(g, g, gn); }
-    gn = sqrtf(teamSum(t, gn));
+    float gn = 0.f, gr = 0.f;
+    TFOR(k, nv) {
+      const float g = Ma[k] - smooth[k] - tmp[k]; grad[k] = g; search[k] = g; gn = fmaf(g, g, gn);
+      const float a = fabsf(Ma[k]) + fabsf(smooth[k]) + fabsf(tmp[k]); gr = fmaf(a, a, gr);
+    }
+    gn = sqrtf(teamSum(t, gn)); gr = sqrtf(teamSum(t, gr));
     TSYNC();
-    if (iter > 0 && scale * gn < D.tolerance) break;
+    // MuJoCo's test (scaled gradient < tolerance = 1e-8) cannot be met in float32: the gradient is a difference of
+    // O(gr) terms and bottoms out near eps * gr, after which further iterations only chase rounding noise.
+    if (iter > 0 && (scale * gn < D.tolerance || gn < GRAD_NOISE * gr)) break;
     if (iter >= D.iterations) { *status |= MYO_WORLD_SOLVER_MAXITER; break; }
     hessianFactor(slot, sm, t, ncon, nefc);
     cholSolve(slot, sm + L.H, search, t);

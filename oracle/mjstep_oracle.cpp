@@ -21,6 +21,8 @@
 //   -> fwdVelocity (ten/actuator velocity, comVel, passive, rne) -> fwdActuation -> fwdAcceleration
 //   -> fwdConstraint (warmstart choice, Newton) -> Euler (implicit joint damping) .
 #include <algorithm>
+#include <cstdio>
+#include <cstdlib>
 #include <atomic>
 #include <thread>
 #include <cmath>
@@ -1297,6 +1299,7 @@ template <typename T> struct Oracle {
       iter++;
       T gn = 0; for (int k = 0; k < n; k++) gn += grad[k] * grad[k];
       T improvement = scale * (oldcost - cost), gradient = scale * std::sqrt(gn);
+      if (getenv("MYO_ORC_TRACE")) fprintf(stderr, "  it %d cost %.9g impr/tol %.3g grad/tol %.3g relimpr %.3g\n", iter, (double)cost, (double)(improvement / tolerance), (double)(gradient / tolerance), (double)((oldcost - cost) / (std::fabs(cost) + 1e-30)));
       if (improvement < tolerance || gradient < tolerance) break;
     }
     solver_niter[0] = iter;
