@@ -168,6 +168,7 @@ typedef enum myo_field {
   MYO_F_EFC_TYPE,        /* [njmax] int32 (mjtConstraint) */
   MYO_F_SOLVER_NITER,    /* [1] int32 */
   MYO_F_STATUS,          /* [1] int32, MYO_WORLD_* bits, sticky until myo_reset */
+  MYO_F_QFRC_APPLIED,    /* [nv]   optional input (mjData.qfrc_applied): added to qfrc_smooth when bound */
   MYO_F_COUNT
 } myo_field;
 

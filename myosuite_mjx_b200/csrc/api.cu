@@ -57,7 +57,7 @@ const char* kFieldNames[MYO_F_COUNT] = {
     "qfrc_passive", "qfrc_spring", "qfrc_damper", "qfrc_actuator", "qfrc_smooth", "qfrc_constraint", "qfrc_inverse", "ncon",
     "nefc", "contact_geom", "contact_dim", "contact_efc_address", "contact_dist", "contact_pos", "contact_frame",
     "contact_includemargin", "contact_friction", "contact_solref", "contact_solimp", "efc_J", "efc_pos", "efc_margin", "efc_D",
-    "efc_aref", "efc_force", "efc_type", "solver_niter", "status"};
+    "efc_aref", "efc_force", "efc_type", "solver_niter", "status", "qfrc_applied"};
 
 bool isIntField(int f) {
   switch (f) {
@@ -72,7 +72,7 @@ int64_t fieldCount(const DevModel& D, int f) {
     case MYO_F_QPOS: return D.nq;
     case MYO_F_QVEL: case MYO_F_QACC_WARMSTART: case MYO_F_QACC: case MYO_F_QACC_SMOOTH: case MYO_F_QLDIAGINV: case MYO_F_QFRC_BIAS:
     case MYO_F_QFRC_PASSIVE: case MYO_F_QFRC_SPRING: case MYO_F_QFRC_DAMPER: case MYO_F_QFRC_ACTUATOR: case MYO_F_QFRC_SMOOTH:
-    case MYO_F_QFRC_CONSTRAINT: case MYO_F_QFRC_INVERSE: return nv;
+    case MYO_F_QFRC_CONSTRAINT: case MYO_F_QFRC_INVERSE: case MYO_F_QFRC_APPLIED: return nv;
     case MYO_F_ACT: case MYO_F_ACT_DOT: return D.na;
     case MYO_F_CTRL: case MYO_F_ACTUATOR_LENGTH: case MYO_F_ACTUATOR_VELOCITY: case MYO_F_ACTUATOR_FORCE: return D.nu;
     case MYO_F_TIME: case MYO_F_NCON: case MYO_F_NEFC: case MYO_F_SOLVER_NITER: case MYO_F_STATUS: return 1;

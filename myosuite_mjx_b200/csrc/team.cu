@@ -184,7 +184,7 @@ __device__ __forceinline__ int teamBcastI(Tm t, int v, int src) { return __shfl_
 
 // batched field access, struct-of-arrays, world fastest: element k of world w lives at base[k * nworld + w]
 struct World { size_t w, nw; };
-#define OUTF(ptr, k) ((float*)(ptr))[(size_t)(k) * W.nw + W.w]
+#define OUTF(ptr, k) ((float*)(ptr))[(size_t)(k) * W.nw + W.w]   /* also used to READ input fields */
 #define OUTI(ptr, k) ((int*)(ptr))[(size_t)(k) * W.nw + W.w]
 
 // ------------------------------------------------------------------------------------------ kinematics
@@ -905,12 +905,13 @@ __device__ __noinline__ void actuation(int slot, int fslot, SP sm, Tm t, World W
   }
   TSYNC();
   // qfrc_actuator = moment^T force through the sparse tendon rows (column view), deterministic gathers
+  const void* applied = tP[slot].F.p[MYO_F_QFRC_APPLIED];   // input: always the batch's own slot
   TFOR(i, nv) {
     float acc = 0.f;
     for (int c = D.col_start[i]; c < D.col_start[i + 1]; c++) { const int n = D.col_nz[c]; acc = fmaf(sm[L.tenJ + n], sm[L.tforce + D.nz_tendon[n]], acc); }
     for (int q = D.dact_start[i]; q < D.dact_start[i + 1]; q++) { const int a = D.dact_list[q]; acc += D.act_gear[a] * sm[L.actforce + a]; }
     sm[L.qfrc_act + i] = acc;
-    const float sf = sm[L.passive + i] - sm[L.bias + i] + acc;
+    const float sf = sm[L.passive + i] - sm[L.bias + i] + acc + (applied ? OUTF(applied, i) : 0.f);
     sm[L.smooth + i] = sf; sm[L.qacc_smooth + i] = sf;
   }
   TSYNC();
@@ -1454,19 +1455,34 @@ __device__ __noinline__ void hessianFactor(int slot, SP sm, Tm t, int ncon, int 
       }
     if (Wnn == 0.f) continue;
     auto Jn = sm + L.conJ + (c * nb) * nv;
-    TFOR(r, nv) {   // each lane owns whole rows of H: no write conflicts, no sync between contacts
+    // the contact Jacobian is non-zero only on dofs that move exactly one of the two bodies: walk that bit set
+    // (static per pair); lane tl owns the tl-th, (tl + TEAM)-th ... non-zero row of H -- no write conflicts
+    const int pr = __float_as_int(cr[7]);
+    const int f1 = D.cg_frame[D.pair_cg1[pr]], f2 = D.cg_frame[D.pair_cg2[pr]];
+    const unsigned long long mx = ((unsigned long long)(unsigned)(D.fr_mask[2 * f1 + 1] ^ D.fr_mask[2 * f2 + 1]) << 32) |
+                                  (unsigned)(D.fr_mask[2 * f1] ^ D.fr_mask[2 * f2]);
+    unsigned long long rows = mx;
+    int idx = 0;
+    #pragma unroll 1
+    while (rows) {
+      const int r = __ffsll((long long)rows) - 1;
+      rows &= rows - 1;
+      if ((idx++ % TEAM) != t.tl) continue;
       const float jn = Jn[r];
       float un = Wnn * jn, ut[3] = {0.f, 0.f, 0.f};
-      bool any = jn != 0.f;
+      #pragma unroll 1
       for (int k = 1; k < dim; k++) {
         const float jt = Jn[k * nv + r];
         un = fmaf(Wnt[k - 1], jt, un); ut[k - 1] = fmaf(Wnt[k - 1], jn, Wtt[k - 1] * jt);
-        any |= jt != 0.f;
       }
-      if (!any) continue;
-      for (int cc = 0; cc <= r; cc++) {
+      unsigned long long cols = mx & ((2ull << r) - 1ull);
+      #pragma unroll 1
+      while (cols) {
+        const int cc = __ffsll((long long)cols) - 1;
+        cols &= cols - 1;
         float acc = fmaf(un, Jn[cc], H[r * nv + cc]);
-        for (int k = 1; k < dim; k++) acc = fmaf(ut[k - 1], Jn[k * nv + cc], acc);
+        if (dim > 1) { acc = fmaf(ut[0], Jn[nv + cc], acc); acc = fmaf(ut[1], Jn[2 * nv + cc], acc); }
+        if (dim > 3) acc = fmaf(ut[2], Jn[3 * nv + cc], acc);
         H[r * nv + cc] = acc;
       }
     }
@@ -1728,7 +1744,11 @@ __device__ __noinline__ void resetState(int slot, SP sm, Tm t) {
 // The warps of a CTA walk the phases of the step together (a CTA barrier between phases): the step is several
 // hundred KB of SASS, far beyond the instruction caches, and keeping an SM's warps inside the same few KB of code
 // removes most instruction-fetch stalls.  Teams still diverge freely inside a phase (contacts, solver iterations).
+#ifdef NO_PHASE_SYNC
+#define PHASE_SYNC() do { } while (0)
+#else
 #define PHASE_SYNC() __syncthreads()
+#endif
 // mj_forward for one world: everything from the state in the scratch
 __device__ __forceinline__ void forwardWorld(int slot, int fslot, SP sm, Tm t, World W, bool live, bool last, int* status, int* ncon_o, int* nefc_o, int* niter_o) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;

@@ -30,6 +30,7 @@ from . import mjcf as _mjcf
 STATE_FIELDS = ("qpos", "qvel", "act", "ctrl", "time", "qacc_warmstart", "status")
 # the subset a policy loop needs ("mode B" in DESIGN.md)
 CORE_FIELDS = STATE_FIELDS + ("qacc", "actuator_force", "actuator_length", "actuator_velocity")
+INPUT_FIELDS = ("qfrc_applied",)   # optional inputs: bound only on request (an unbound input reads as zero)
 
 _SHAPES = {
     "xpos": ("nbody", 3), "xquat": ("nbody", 4), "xmat": ("nbody", 9), "xipos": ("nbody", 3), "ximat": ("nbody", 9),
@@ -81,11 +82,11 @@ class Data:
         self._t = {}
         dev = torch.device("cuda", model.device)
         if fields == "all":
-            names = [n.lower() for n in _desc.FIELD_NAMES]
+            names = [n.lower() for n in _desc.FIELD_NAMES if n.lower() not in INPUT_FIELDS]
         elif fields == "core":
             names = list(CORE_FIELDS)
         else:
-            names = list(dict.fromkeys(list(STATE_FIELDS) + list(fields)))
+            names = list(dict.fromkeys(list(STATE_FIELDS) + [f.lower() for f in fields]))
         for name in names:
             fid = _desc.FIELD_ID[name]
             cnt = L.myo_field_count(h, fid)
@@ -159,6 +160,9 @@ def put_model(mj_model, device=0) -> Model:
     real mujoco.MjModel."""
     if isinstance(mj_model, str):
         mj_model = _mjcf.from_xml_path(mj_model)
+    from . import lengthrange as _lr
+    if len(_lr.needs_length_range(mj_model)):      # MuJoCo does this inside mj_loadXML (mj_setLengthRange)
+        _lr.set_length_range(mj_model, device=device)
     return Model(mj_model, device)
 
 

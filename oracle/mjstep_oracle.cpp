@@ -412,7 +412,7 @@ template <typename T> struct Oracle {
   std::vector<T> xpos, xquat, xmat, xipos, ximat, xanchor, xaxis, geom_xpos, geom_xmat, site_xpos, site_xmat, subtree_com,
       cinert, crb, cdof, cdof_dot, cvel, ten_length, ten_velocity, ten_J, wrap_xpos, actuator_length, actuator_velocity,
       actuator_moment, actuator_force, act_dot, qM, qLD, qLDiagInv, qMdense, qLDdense, qfrc_bias, qfrc_passive, qfrc_spring,
-      qfrc_damper, qfrc_actuator, qfrc_smooth, qfrc_constraint, qfrc_inverse, qacc, qacc_smooth;
+      qfrc_damper, qfrc_actuator, qfrc_smooth, qfrc_constraint, qfrc_inverse, qacc, qacc_smooth, qfrc_applied;
   std::vector<int32_t> ten_wrapadr, ten_wrapnum, wrap_obj;
   std::vector<Contact<T>> contacts;
   // exported flat contact / efc arrays
@@ -437,7 +437,7 @@ template <typename T> struct Oracle {
     actuator_moment.assign((size_t)nu * nv, 0); actuator_force.assign(nu, 0); act_dot.assign(na, 0); qM.assign(nM, 0);
     qLD.assign(nM, 0); qLDiagInv.assign(nv, 0); qMdense.assign((size_t)nv * nv, 0); qLDdense.assign((size_t)nv * nv, 0);
     for (auto* v : {&qfrc_bias, &qfrc_passive, &qfrc_spring, &qfrc_damper, &qfrc_actuator, &qfrc_smooth, &qfrc_constraint,
-                    &qfrc_inverse, &qacc, &qacc_smooth}) v->assign(nv, 0);
+                    &qfrc_inverse, &qacc, &qacc_smooth, &qfrc_applied}) v->assign(nv, 0);
     ncon_v.assign(1, 0); nefc_v.assign(1, 0); solver_niter.assign(1, 0); status.assign(1, 0); solver_cost.assign(1, 0);
     reset();
 #define REG(f) fields[#f] = {(void*)f.data(), {(int64_t)f.size(), 0}}
@@ -447,7 +447,7 @@ template <typename T> struct Oracle {
     REG(cinert); REG(crb); REG(cdof); REG(cdof_dot); REG(cvel); REG(ten_length); REG(ten_velocity); REG(ten_J); REG(wrap_xpos);
     REG(actuator_length); REG(actuator_velocity); REG(actuator_moment); REG(actuator_force); REG(act_dot); REG(qM); REG(qLD);
     REG(qLDiagInv); REG(qMdense); REG(qLDdense); REG(qfrc_bias); REG(qfrc_passive); REG(qfrc_spring); REG(qfrc_damper);
-    REG(qfrc_actuator); REG(qfrc_smooth); REG(qfrc_constraint); REG(qfrc_inverse); REG(qacc); REG(qacc_smooth);
+    REG(qfrc_actuator); REG(qfrc_applied); REG(qfrc_smooth); REG(qfrc_constraint); REG(qfrc_inverse); REG(qacc); REG(qacc_smooth);
     REGI(ten_wrapadr); REGI(ten_wrapnum); REGI(wrap_obj); REGI(ncon_v); REGI(nefc_v); REGI(solver_niter); REGI(status);
     REG(solver_cost);
   }
@@ -463,6 +463,7 @@ template <typename T> struct Oracle {
     for (int i = 0; i < nq; i++) qpos[i] = T(m.qpos0[i]);
     std::fill(qvel.begin(), qvel.end(), T(0)); std::fill(act.begin(), act.end(), T(0));
     std::fill(ctrl.begin(), ctrl.end(), T(0)); std::fill(qacc_warmstart.begin(), qacc_warmstart.end(), T(0));
+    std::fill(qfrc_applied.begin(), qfrc_applied.end(), T(0));
     time[0] = 0; status[0] = 0;
   }
 
@@ -1157,7 +1158,7 @@ template <typename T> struct Oracle {
   }
 
   void fwdAcceleration() {
-    for (int i = 0; i < nv; i++) { qfrc_smooth[i] = qfrc_passive[i] - qfrc_bias[i] + qfrc_actuator[i]; qacc_smooth[i] = qfrc_smooth[i]; }
+    for (int i = 0; i < nv; i++) { qfrc_smooth[i] = qfrc_passive[i] - qfrc_bias[i] + qfrc_actuator[i] + qfrc_applied[i]; qacc_smooth[i] = qfrc_smooth[i]; }
     solveSparse(qLD, qLDiagInv, qacc_smooth.data());
   }
 

@@ -104,3 +104,16 @@ def test_step_host_round_trip(models):
     mjx.step(model, e, 3)
     torch.cuda.synchronize()
     assert torch.equal(oq, e.storage("qpos").cpu()) and torch.equal(ov, e.storage("qvel").cpu()) and torch.equal(oa, e.storage("act").cpu())
+
+
+def test_length_range_simulation_on_device(models):
+    """mj_setLengthRange on the GPU (put_model does it for models without lengthrange): reproduces the fixture."""
+    import copy
+    from myosuite_mjx_b200 import lengthrange
+    m = copy.copy(models("finger"))
+    want = np.asarray(m.actuator_lengthrange, dtype=np.float64).reshape(-1, 2).copy()
+    m.actuator_lengthrange = np.zeros_like(want)
+    assert len(lengthrange.needs_length_range(m)) == m.nu
+    ids, rng, spread = lengthrange.set_length_range(m)
+    np.testing.assert_allclose(rng, want, rtol=1e-5, atol=1e-7)
+    assert spread.max() < 1e-4

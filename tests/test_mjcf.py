@@ -45,9 +45,8 @@ def test_structural_invariants(models, name):
     lim = np.asarray(m.jnt_limited).astype(bool)
     r = np.asarray(m.jnt_range)
     assert np.all(r[lim, 0] < r[lim, 1])
-    if name != "finger":   # finger: compile-time length-range simulation (mj_setLengthRange) -- see DESIGN.md
-        lr = np.asarray(m.actuator_lengthrange)
-        assert np.all(lr[:, 0] < lr[:, 1])
+    lr = np.asarray(m.actuator_lengthrange)      # finger: filled by the compile-time simulation (tests/test_lengthrange.py)
+    assert np.all(lr[:, 0] < lr[:, 1])
 
 
 def test_hand_known_values(models):

@@ -17,7 +17,7 @@ STAGE_FIELDS = ["xpos", "xquat", "xmat", "xipos", "ximat", "xanchor", "xaxis", "
                 "subtree_com", "cinert", "crb", "cdof", "cdof_dot", "cvel", "ten_length", "ten_velocity", "ten_J",
                 "actuator_length", "actuator_velocity", "actuator_moment", "actuator_force", "act_dot", "qM", "qLDiagInv",
                 "qfrc_bias", "qfrc_passive", "qfrc_spring", "qfrc_damper", "qfrc_actuator", "qfrc_smooth", "qacc_smooth"]
-MODELS = ["elbow", "hand", "hand_pose", "hand_sar", "legs"]
+MODELS = ["elbow", "finger", "hand", "hand_pose", "hand_sar", "legs"]
 
 
 @pytest.fixture(scope="module")
