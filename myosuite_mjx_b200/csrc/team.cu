@@ -466,7 +466,8 @@ __device__ __noinline__ float wrapCircle(float* pnt, const float* d, const float
   const float n0 = fmaxf(MINVAL, sqrtf(pnt[0] * pnt[0] + pnt[1] * pnt[1])), n1 = fmaxf(MINVAL, sqrtf(pnt[2] * pnt[2] + pnt[3] * pnt[3]));
   float ang = acos_(clipf((pnt[0] * pnt[2] + pnt[1] * pnt[3]) / (n0 * n1), -1.f, 1.f));
   const float cr = pnt[1] * pnt[2] - pnt[0] * pnt[3];
-  if ((cr > 0.f && i) || (cr < 0.f && !i)) ang = 2.f * CUDART_PI_F - ang;
+  // coincident tangent points (grazing path): cr is rounding noise there and must not flip a ~0 arc into a ~2 pi one
+  if (fabsf(cr) > 1e-5f * sqr && ((cr > 0.f && i) || (cr < 0.f && !i))) ang = 2.f * CUDART_PI_F - ang;
   return rad * ang;
 }
 __device__ __noinline__ float wrapInside(float* pnt, const float* d, float rad) {

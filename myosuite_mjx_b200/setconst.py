@@ -48,7 +48,8 @@ def _arc(p0, p1, ind):
     b = p1 / max(np.linalg.norm(p1), MINVAL)
     ang = math.acos(min(1.0, max(-1.0, float(a @ b))))
     cr = p0[1] * p1[0] - p0[0] * p1[1]
-    if (cr > 0 and ind) or (cr < 0 and not ind):
+    # grazing path: cr is rounding noise and must not turn a ~0 arc into a ~2 pi one (same guard as the kernel)
+    if abs(cr) > 1e-5 * np.linalg.norm(p0) * np.linalg.norm(p1) and ((cr > 0 and ind) or (cr < 0 and not ind)):
         ang = 2 * math.pi - ang
     return ang
 

@@ -138,7 +138,10 @@ template <typename T> T arcAngle(const T* p0, const T* p1, int ind) {
   T c = clip((p0[0] * p1[0] + p0[1] * p1[1]) / (n0 * n1), T(-1), T(1));
   T ang = std::acos(c);
   T cr = p0[1] * p1[0] - p0[0] * p1[1];
-  if ((cr > 0 && ind) || (cr < 0 && !ind)) ang = T(2 * M_PI) - ang;
+  // Grazing path (coincident tangent points): cr is pure rounding noise there and a sign test on it would turn a ~0 arc
+  // into a ~2 pi one -- a measure-zero discontinuity of the published recipe (hit e.g. by a joint sitting exactly on
+  // its range limit).  Both this restatement and the CUDA kernel ignore cr below 1e-5 * |p0| |p1|.
+  if (std::fabs(cr) > T(1e-5) * n0 * n1 && ((cr > 0 && ind) || (cr < 0 && !ind))) ang = T(2 * M_PI) - ang;
   return ang;
 }
 // returns arc length or -1; pnt = two tangent points (2-D)
