@@ -17,4 +17,4 @@ for i in range(int(sys.argv[1]) if len(sys.argv) > 1 else 60):
     if i % 10 == 9:
         torch.cuda.synchronize()
         nc, ne, ni = d.ncon.cpu().numpy().ravel(), d.nefc.cpu().numpy().ravel(), d.solver_niter.cpu().numpy().ravel()
-        print(f"step {i+1}: ncon mean {nc.mean():.2f} p50 {np.median(nc)} p99 {np.percentile(nc,99)} max {nc.max()} | nefc mean {ne.mean():.1f} p99 {np.percentile(ne,99)} max {ne.max()} | niter mean {ni.mean():.2f} hist {np.bincount(ni)[:12]} | flagged {(d.status.cpu().numpy()!=0).sum()}")
+        print(f"step {i+1}: ncon mean {nc.mean():.2f} p50 {np.median(nc)} p99 {np.percentile(nc,99)} max {nc.max()} | nefc mean {ne.mean():.1f} p99 {np.percentile(ne,99)} max {ne.max()} | niter mean {ni.mean():.2f} hist {np.bincount(ni)[:12]} | flagged {(d.status.cpu().numpy()!=0).sum()} bits {[(b, int(((d.status.cpu().numpy() & b)!=0).sum())) for b in (1,2,4,8,16,32)]}")
