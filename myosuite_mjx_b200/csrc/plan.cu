@@ -584,9 +584,10 @@ void myo_build_plan(const myo_model_desc& m, int nconmax_req, int njmax_req, Dev
 void myo_make_layout(DevModel& D, int nconmax_req, int njmax_req, SmemLayout& L) {
   const int nv = D.nv;
   int maxcon = 2 * D.npair;  // 2 contacts per plane-capsule pair, 1 otherwise
-  D.nconmax = nconmax_req > 0 ? nconmax_req : std::min(maxcon, 16);
+  // defaults sized from the MyoHand random-ctrl rollout (fist clench): max 27 contacts / 123 rows over 8192 worlds x 1000 steps
+  D.nconmax = nconmax_req > 0 ? nconmax_req : std::min(maxcon, 32);
   int maxrows = D.neq + 2 * D.nlimj + 2 * D.nlimt + D.nconmax * (D.maxbase == 1 ? 1 : 2 * (D.maxbase - 1));
-  D.njmax = njmax_req > 0 ? njmax_req : std::min(maxrows, 96);
+  D.njmax = njmax_req > 0 ? njmax_req : std::min(maxrows, 160);
   if (D.njmax < D.neq) throw std::string("njmax smaller than the number of equality rows");
   const int nb = D.maxbase;  // base Jacobian rows per contact (normal, 2 tangents, torsion)
   int o = 0;

@@ -1523,19 +1523,28 @@ __device__ __noinline__ void cholSolve(int slot, SP H, SP x, Tm t) {
     TSYNC();
   }
 }
-struct LsPt { float alpha, cost, d0, d1; };
-__device__ __noinline__ LsPt lsEval(int slot, SP sm, Tm t, int nefc, float a, const float* qg) {
+// One point of the 1-D cost along the search direction.  `tol` is the convergence threshold for |d0| at this point:
+// MuJoCo's gtol, or the float32 noise floor of the derivative sum when that is larger (the sum cancels to ~eps * mag
+// at the minimiser; without the floor the search burns all ls_iterations chasing rounding noise -- measured on the
+// float build of the oracle: 34 evaluations per search instead of the double build's 2.8).
+#ifndef LS_NOISE
+#define LS_NOISE 2e-6f
+#endif
+struct LsPt { float alpha, cost, d0, d1, tol; };
+__device__ __noinline__ LsPt lsEval(int slot, SP sm, Tm t, int nefc, float a, const float* qg, float gtol) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
-  float q0 = 0.f, q1 = 0.f, q2 = 0.f;
+  float q0 = 0.f, q1 = 0.f, q2 = 0.f, qa = 0.f;
+  const int neq = D.neq;
   TFOR(r, nefc) {
     const float jar = EFC(E_JAR, r), jv = EFC(E_JV, r), x = fmaf(a, jv, jar);
-    if (rowOn(EFCI(E_DESC0, r), x)) {
-      const float Dr = EFC(E_D, r);
-      q0 = fmaf(0.5f * Dr * jar, jar, q0); q1 = fmaf(Dr * jar, jv, q1); q2 = fmaf(0.5f * Dr * jv, jv, q2);
+    if (r < neq || x < 0.f) {   // equality rows come first and are always active
+      const float Dr = EFC(E_D, r), dj = Dr * jar;
+      q0 = fmaf(0.5f * dj, jar, q0); q1 = fmaf(dj, jv, q1); q2 = fmaf(0.5f * Dr * jv, jv, q2); qa = fmaf(fabsf(dj), fabsf(jv), qa);
     }
   }
-  q0 = teamSum(t, q0) + qg[0]; q1 = teamSum(t, q1) + qg[1]; q2 = teamSum(t, q2) + qg[2];
+  q0 = teamSum(t, q0) + qg[0]; q1 = teamSum(t, q1) + qg[1]; q2 = teamSum(t, q2) + qg[2]; qa = teamSum(t, qa) + fabsf(qg[1]);
   LsPt p; p.alpha = a; p.cost = a * a * q2 + a * q1 + q0; p.d0 = 2.f * a * q2 + q1; p.d1 = 2.f * q2;
+  p.tol = fmaxf(gtol, LS_NOISE * (qa + 2.f * fabsf(a) * q2));
   if (p.d1 <= 0.f) p.d1 = MINVAL;
   return p;
 }
@@ -1600,18 +1609,18 @@ __device__ __noinline__ int solveNewton(int slot, SP sm, Tm t, int ncon, int nef
     const float qg[3] = {gauss, teamSum(t, g1), teamSum(t, g2)};
     const float gtol = D.tolerance * D.ls_tolerance * sn / scale;
     int lsiter = 0;
-    LsPt p0 = lsEval(slot, sm, t, nefc, 0.f, qg); lsiter++;
-    LsPt p1 = lsEval(slot, sm, t, nefc, p0.alpha - p0.d0 / p0.d1, qg); lsiter++;
+    LsPt p0 = lsEval(slot, sm, t, nefc, 0.f, qg, gtol); lsiter++;
+    LsPt p1 = lsEval(slot, sm, t, nefc, p0.alpha - p0.d0 / p0.d1, qg, gtol); lsiter++;
     if (p0.cost < p1.cost) p1 = p0;
-    bool done = fabsf(p1.d0) < gtol;
+    bool done = fabsf(p1.d0) < p1.tol;
     if (!done) {
       const float dir = p1.d0 < 0.f ? 1.f : -1.f;
       LsPt p2 = p1; bool have2 = false;
       // #pragma unroll 1
-      while (p1.d0 * dir <= -gtol && lsiter < D.ls_iterations) {
+      while (p1.d0 * dir <= -p1.tol && lsiter < D.ls_iterations) {
         p2 = p1; have2 = true;
-        p1 = lsEval(slot, sm, t, nefc, p1.alpha - p1.d0 / p1.d1, qg); lsiter++;
-        if (fabsf(p1.d0) < gtol) { done = true; break; }
+        p1 = lsEval(slot, sm, t, nefc, p1.alpha - p1.d0 / p1.d1, qg, gtol); lsiter++;
+        if (fabsf(p1.d0) < p1.tol) { done = true; break; }
       }
       if (!done && lsiter < D.ls_iterations && have2) {
         LsPt lo = p2, hi = p1;
@@ -1622,12 +1631,12 @@ __device__ __noinline__ int solveNewton(int slot, SP sm, Tm t, int ncon, int nef
           const float ca[3] = {lo.alpha - lo.d0 / lo.d1, hi.alpha - hi.d0 / hi.d1, 0.5f * (lo.alpha + hi.alpha)};
           LsPt cand[3];
           // #pragma unroll 1
-          for (int q = 0; q < 3; q++) { cand[q] = lsEval(slot, sm, t, nefc, ca[q], qg); lsiter++; }
+          for (int q = 0; q < 3; q++) { cand[q] = lsEval(slot, sm, t, nefc, ca[q], qg, gtol); lsiter++; }
           // #pragma unroll 1
           for (int q = 0; q < 3; q++) {
             if (done) break;
             const LsPt c = cand[q];
-            if (fabsf(c.d0) < gtol) { p1 = c; done = true; break; }
+            if (fabsf(c.d0) < c.tol) { p1 = c; done = true; break; }
             if (!((c.alpha - lo.alpha) * dir > 0.f && (hi.alpha - c.alpha) * dir > 0.f)) continue;
             if (c.d0 * dir < 0.f) lo = c; else hi = c;
             moved = true;

@@ -30,6 +30,7 @@
 #include <cstring>
 #include <map>
 #include <string>
+#include <limits>
 #include <vector>
 
 #include "../include/myostep.h"
@@ -1245,30 +1246,37 @@ template <typename T> struct Oracle {
         T qg[3] = {gauss, 0, 0};
         for (int k = 0; k < n; k++) { qg[1] += search[k] * (Ma[k] - qfrc_smooth[k]); qg[2] += T(0.5) * search[k] * Mv[k]; }
         const T gtol = tolerance * lstol * snorm / scale;
-        struct Pt { T alpha, cost, d0, d1; };
+        // tol: MuJoCo's gtol, or the rounding-noise floor of the derivative sum in the scalar type when that is larger
+        // (16 eps * magnitude of the cancelling terms: 2e-6 in float32 -- the CUDA kernel's LS_NOISE -- and 3.6e-15 in
+        // double, where it never binds).  Without it the float32 search runs to ls_iterations on rounding noise.
+        struct Pt { T alpha, cost, d0, d1, tol; };
+        const T lsnoise = T(16) * std::numeric_limits<T>::epsilon();
         int lsiter = 0;
         auto eval = [&](T a) {
-          T q0 = qg[0], q1 = qg[1], q2 = qg[2];
+          T q0 = qg[0], q1 = qg[1], q2 = qg[2], qa = std::fabs(qg[1]);
           for (int i = 0; i < nefc; i++) {
             T x = jar[i] + a * Jv[i];
-            if (rowIsEquality(i) || x < 0) { q0 += T(0.5) * efc_D[i] * jar[i] * jar[i]; q1 += efc_D[i] * jar[i] * Jv[i]; q2 += T(0.5) * efc_D[i] * Jv[i] * Jv[i]; }
+            if (rowIsEquality(i) || x < 0) {
+              q0 += T(0.5) * efc_D[i] * jar[i] * jar[i]; q1 += efc_D[i] * jar[i] * Jv[i]; q2 += T(0.5) * efc_D[i] * Jv[i] * Jv[i];
+              qa += std::fabs(efc_D[i] * jar[i] * Jv[i]);
+            }
           }
           lsiter++;
-          Pt p{a, a * a * q2 + a * q1 + q0, 2 * a * q2 + q1, 2 * q2};
+          Pt p{a, a * a * q2 + a * q1 + q0, 2 * a * q2 + q1, 2 * q2, std::max(gtol, lsnoise * (qa + 2 * std::fabs(a) * q2))};
           if (p.d1 <= 0) p.d1 = T(kMinVal);
           return p;
         };
         Pt p0 = eval(0);
         Pt p1 = eval(p0.alpha - p0.d0 / p0.d1);
         if (p0.cost < p1.cost) p1 = p0;
-        bool done = std::fabs(p1.d0) < gtol;
+        bool done = std::fabs(p1.d0) < p1.tol;
         if (!done) {
           const T dir = p1.d0 < 0 ? T(1) : T(-1);
           Pt p2 = p1; bool have2 = false;
-          while (p1.d0 * dir <= -gtol && lsiter < m.opt_ls_iterations) {
+          while (p1.d0 * dir <= -p1.tol && lsiter < m.opt_ls_iterations) {
             p2 = p1; have2 = true;
             p1 = eval(p1.alpha - p1.d0 / p1.d1);
-            if (std::fabs(p1.d0) < gtol) { done = true; break; }
+            if (std::fabs(p1.d0) < p1.tol) { done = true; break; }
           }
           if (!done && lsiter < m.opt_ls_iterations && have2) {
             // bracket: p2 still descends along dir, p1 has overshot
@@ -1278,7 +1286,7 @@ template <typename T> struct Oracle {
               bool moved = false;
               Pt best = lo.cost < hi.cost ? lo : hi;
               for (auto& c : cand) {
-                if (std::fabs(c.d0) < gtol) { p1 = c; done = true; break; }
+                if (std::fabs(c.d0) < c.tol) { p1 = c; done = true; break; }
                 bool insideBr = (c.alpha - lo.alpha) * dir > 0 && (hi.alpha - c.alpha) * dir > 0;
                 if (!insideBr) continue;
                 if (c.d0 * dir < 0) { lo = c; moved = true; } else { hi = c; moved = true; }
@@ -1291,6 +1299,7 @@ template <typename T> struct Oracle {
           }
         }
         alpha = p1.alpha;
+        if (getenv("MYO_ORC_TRACE")) fprintf(stderr, "  linesearch evals %d alpha %.9g d0 %.3g gtol %.3g\n", lsiter, (double)alpha, (double)p1.d0, (double)gtol);
       }
       if (alpha == 0) break;
       for (int k = 0; k < n; k++) { qacc[k] += alpha * search[k]; Ma[k] += alpha * Mv[k]; }

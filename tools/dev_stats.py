@@ -9,7 +9,7 @@ m = bench.load_model("hand")
 model = mjx.put_model(m)
 nw = 8192
 q0 = bench.initial_qpos(m, nw, 1234)
-d = mjx.put_data(model, dict(qpos=q0), nworld=nw, fields=("ncon", "nefc", "solver_niter", "qacc"))
+d = mjx.put_data(model, dict(qpos=q0), nworld=nw, fields=("ncon", "nefc", "solver_niter", "qacc"), nconmax=int(os.environ.get("NCONMAX", 0)), njmax=int(os.environ.get("NJMAX", 0)))
 gen = torch.Generator(device="cuda"); gen.manual_seed(1234)
 for i in range(int(sys.argv[1]) if len(sys.argv) > 1 else 60):
     if i % 10 == 0: d.storage("ctrl").uniform_(0, 1, generator=gen)
