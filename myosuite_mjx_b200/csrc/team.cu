@@ -1456,19 +1456,16 @@ __device__ __noinline__ void hessianFactor(int slot, SP sm, Tm t, int ncon, int 
       }
     if (Wnn == 0.f) continue;
     auto Jn = sm + L.conJ + (c * nb) * nv;
-    // the contact Jacobian is non-zero only on dofs that move exactly one of the two bodies: walk that bit set
-    // (static per pair); lane tl owns the tl-th, (tl + TEAM)-th ... non-zero row of H -- no write conflicts
+    // The contact Jacobian is non-zero only on dofs that move exactly one of the two bodies: that bit set is static per
+    // pair.  Lane tl owns the tl-th, (tl + TEAM)-th ... set bit as a row of H and finds it directly (__fns), so the
+    // lanes of a team work on their rows at the same time; columns are the set bits up to the row.
     const int pr = __float_as_int(cr[7]);
     const int f1 = D.cg_frame[D.pair_cg1[pr]], f2 = D.cg_frame[D.pair_cg2[pr]];
-    const unsigned long long mx = ((unsigned long long)(unsigned)(D.fr_mask[2 * f1 + 1] ^ D.fr_mask[2 * f2 + 1]) << 32) |
-                                  (unsigned)(D.fr_mask[2 * f1] ^ D.fr_mask[2 * f2]);
-    unsigned long long rows = mx;
-    int idx = 0;
+    const unsigned mlo = (unsigned)(D.fr_mask[2 * f1] ^ D.fr_mask[2 * f2]), mhi = (unsigned)(D.fr_mask[2 * f1 + 1] ^ D.fr_mask[2 * f2 + 1]);
+    const int nlo = __popc(mlo), nrow = nlo + __popc(mhi);
     #pragma unroll 1
-    while (rows) {
-      const int r = __ffsll((long long)rows) - 1;
-      rows &= rows - 1;
-      if ((idx++ % TEAM) != t.tl) continue;
+    for (int a = t.tl; a < nrow; a += TEAM) {
+      const int r = a < nlo ? (int)__fns(mlo, 0, a + 1) : 32 + (int)__fns(mhi, 0, a + 1 - nlo);
       const float jn = Jn[r];
       float un = Wnn * jn, ut[3] = {0.f, 0.f, 0.f};
       #pragma unroll 1
@@ -1476,17 +1473,25 @@ __device__ __noinline__ void hessianFactor(int slot, SP sm, Tm t, int ncon, int 
         const float jt = Jn[k * nv + r];
         un = fmaf(Wnt[k - 1], jt, un); ut[k - 1] = fmaf(Wnt[k - 1], jn, Wtt[k - 1] * jt);
       }
-      unsigned long long cols = mx & ((2ull << r) - 1ull);
+      auto Hr = H + r * nv;
       #pragma unroll 1
-      while (cols) {
-        const int cc = __ffsll((long long)cols) - 1;
-        cols &= cols - 1;
-        float acc = fmaf(un, Jn[cc], H[r * nv + cc]);
-        if (dim > 1) { acc = fmaf(ut[0], Jn[nv + cc], acc); acc = fmaf(ut[1], Jn[2 * nv + cc], acc); }
-        if (dim > 3) acc = fmaf(ut[2], Jn[3 * nv + cc], acc);
-        H[r * nv + cc] = acc;
+      for (int half = 0; half < 2; half++) {
+        unsigned w;
+        if (half == 0) w = r >= 32 ? mlo : (mlo & ((2u << r) - 1u));
+        else w = r >= 32 ? (mhi & ((2u << (r - 32)) - 1u)) : 0u;
+        #pragma unroll 1
+        while (w) {
+          const int cc = 32 * half + __ffs((int)w) - 1;
+          w &= w - 1u;
+          auto Jc = Jn + cc;
+          float acc = fmaf(un, Jc[0], Hr[cc]);
+          if (dim > 1) { acc = fmaf(ut[0], Jc[nv], acc); acc = fmaf(ut[1], Jc[2 * nv], acc); }
+          if (dim > 3) acc = fmaf(ut[2], Jc[3 * nv], acc);
+          Hr[cc] = acc;
+        }
       }
     }
+    TSYNC();   // row ownership changes with the next contact's bit set
   }
   TSYNC();
   // left-looking Cholesky, lanes over rows
