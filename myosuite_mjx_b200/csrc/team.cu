@@ -1138,19 +1138,62 @@ __device__ __noinline__ int collision(int slot, SP sm, Tm t, int* status) {
     ncand += total;
   }
   TSYNC();
+  // Narrow phase in three sweeps per chunk of survivors, so that the lanes running the (long, branchy, float64) MPR do it
+  // at the same time instead of idling the lanes whose pair had a closed form: (a) closed-form pairs, MPR pairs only
+  // listed; (b) the listed MPR pairs, TEAM at a time; (c) in-order compaction of all hits.  Per-survivor results live in
+  // the solver's scratch (unused until makeConstraint): 16 floats = count, two hits, one list slot.
+  auto tmp = sm + L.conJ;
+  const int cap = max(TEAM, (L.limrow - L.conJ) / 16);
   int ncon = 0;
-  for (int base = 0; base < ncand; base += TEAM) {
-    const int k = base + t.tl;
-    Hit h[2]; int n = 0, pr = 0;
-    if (k < ncand) { pr = cand[k]; n = collidePair(slot, sm, pr, h); }
-    int total; int at = ncon + teamExclScan(t, n, &total);
-    for (int q = 0; q < n; q++, at++) {
-      if (at >= D.nconmax) continue;
-      auto c = sm + L.con + 12 * at;
-      c[0] = h[q].dist; st3(c + 1, h[q].pos); st3(c + 4, h[q].nrm);
-      c[7] = __int_as_float(pr); c[8] = __int_as_float(-1); c[9] = __int_as_float(D.pair_dim[pr]);
+  for (int c0 = 0; c0 < ncand; c0 += cap) {
+    const int cn = min(cap, ncand - c0);
+    int nm = 0;
+    for (int base = 0; base < cn; base += TEAM) {
+      const int k = base + t.tl;
+      bool mp = false;
+      if (k < cn) {
+        const int pr = cand[c0 + k];
+        const int t1 = D.cg_type[D.pair_cg1[pr]], t2 = D.cg_type[D.pair_cg2[pr]];
+        mp = t1 != G_PLANE && !((t1 == G_SPHERE || t1 == G_CAPSULE) && (t2 == G_SPHERE || t2 == G_CAPSULE) && !(t1 == G_CAPSULE && t2 == G_SPHERE));
+        if (!mp) {
+          Hit h[2];
+          const int n = collidePair(slot, sm, pr, h);
+          auto o = tmp + 16 * k;
+          o[0] = __int_as_float(n);
+          for (int q = 0; q < n; q++) { o[1 + 7 * q] = h[q].dist; st3(o + 2 + 7 * q, h[q].pos); st3(o + 5 + 7 * q, h[q].nrm); }
+        }
+      }
+      int total; const int at = nm + teamExclScan(t, mp ? 1 : 0, &total);
+      if (mp) tmp[16 * at + 15] = __int_as_float(k);
+      nm += total;
     }
-    ncon += total;
+    TSYNC();
+    for (int base = 0; base < nm; base += TEAM) {
+      const int j = base + t.tl;
+      if (j < nm) {
+        const int k = __float_as_int(tmp[16 * j + 15]);
+        Hit h[2];
+        const int n = collidePair(slot, sm, cand[c0 + k], h);
+        auto o = tmp + 16 * k;
+        o[0] = __int_as_float(n);
+        if (n) { o[1] = h[0].dist; st3(o + 2, h[0].pos); st3(o + 5, h[0].nrm); }
+      }
+    }
+    TSYNC();
+    for (int base = 0; base < cn; base += TEAM) {
+      const int k = base + t.tl;
+      const int n = k < cn ? __float_as_int(tmp[16 * k]) : 0;
+      int total; int at = ncon + teamExclScan(t, n, &total);
+      for (int q = 0; q < n; q++, at++) {
+        if (at >= D.nconmax) continue;
+        const int pr = cand[c0 + k];
+        auto c = sm + L.con + 12 * at; auto o = tmp + 16 * k + 1 + 7 * q;
+        for (int e = 0; e < 7; e++) c[e] = o[e];
+        c[7] = __int_as_float(pr); c[8] = __int_as_float(-1); c[9] = __int_as_float(D.pair_dim[pr]);
+      }
+      ncon += total;
+    }
+    TSYNC();
   }
   if (ncon > D.nconmax) { *status |= MYO_WORLD_NCON_OVERFLOW; ncon = D.nconmax; }
   TSYNC();
