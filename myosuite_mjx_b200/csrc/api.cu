@@ -39,8 +39,8 @@ const TeamVariant kVariants[] = {
 int64_t g_launches = 0;
 // lanes per world: the step is latency-bound, so small batches get wider teams (more warps per SM)
 const TeamVariant* pickVariant(int nworld) {
-  int team = 16;   // widest team whose warps are all resident at once (16 warps per SM, 148 SMs)
-  while (team > 1 && (int64_t)nworld * team > (int64_t)148 * 16 * 32) team >>= 1;
+  int team = 16;   // widest team whose warps are all resident at once (one 14-warp CTA per SM, 148 SMs)
+  while (team > 1 && (int64_t)nworld * team > (int64_t)148 * 14 * 32) team >>= 1;
   if (const char* e = getenv("MYO_TEAM")) team = atoi(e);
   for (const TeamVariant& v : kVariants) if (v.team == team) return &v;
   return &kVariants[2];

@@ -115,6 +115,8 @@ struct SmemLayout {
   int slots, ulen, uwrap, tmpbody;
   // overlay region B (collision / constraint / solver stage)
   int cgpose, con, conJ, efc, H, nvec, limrow, basev, cand;
+  int nv;        // copy of DevModel.nv (the launch sizes the shared-memory Hessian tiles from it)
+  int hshared;   // set by the kernel variant at upload: Newton Hessian tiles live in shared memory
 };
 
 #endif  // MYO_DEVMODEL_H_

@@ -615,4 +615,5 @@ void myo_make_layout(DevModel& D, int nconmax_req, int njmax_req, SmemLayout& L)
   L.cand = take(D.npair);
   int endB = o;
   L.total = std::max(endA, endB);
+  L.nv = nv; L.hshared = 0;
 }

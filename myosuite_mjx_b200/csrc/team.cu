@@ -139,6 +139,15 @@ struct SPI {
   __device__ __forceinline__ int& operator[](int i) const { return p[i * SCR_STRIDE]; }
 };
 __device__ __forceinline__ SPI asInt(SP s) { SPI r; r.p = (int*)s.p; return r; }
+// Dense Newton Hessian (nv x nv) of this lane's world.  It is the most re-read block of the solver (assembly, Cholesky,
+// two triangular solves per iteration), so it lives in shared memory -- same interleaving as the scratch, one
+// [nv*nv][SCR_STRIDE] tile per warp -- whenever the CTA's tiles fit (hshared, set at upload), else in the scratch.
+extern __shared__ float ctaShared[];
+__device__ __forceinline__ SP hessian(SP sm, int offH, int nv, int hshared) {
+  if (!hshared) return sm + offH;
+  SP r; r.p = ctaShared + (threadIdx.x >> 5) * (nv * nv * SCR_STRIDE) + (threadIdx.x & 31) / TEAM;
+  return r;
+}
 
 // A team of TEAM lanes works on one world; 32 / TEAM worlds share a warp.  Teams of one warp may diverge on data
 // (contacts, solver iterations), so every sync / shuffle names only the team's own lanes.
@@ -1448,7 +1457,7 @@ __device__ __noinline__ void constraintForce(int slot, SP sm, Tm t, int ncon, in
 __device__ __noinline__ void hessianFactor(int slot, SP sm, Tm t, int ncon, int nefc) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
   const int nv = D.nv, nb = D.maxbase;
-  auto H = sm + L.H;
+  auto H = hessian(sm, L.H, nv, L.hshared);
   TFOR(i, nv * nv) H[i] = 0.f;
   TSYNC();
   TFOR(e, D.nM) H[D.M_row[e] * nv + D.M_col[e]] = sm[L.qM + e];
@@ -1639,7 +1648,7 @@ __device__ __noinline__ int solveNewton(int slot, SP sm, Tm t, int ncon, int nef
     if (iter > 0 && (scale * gn < D.tolerance || gn < GRAD_NOISE * gr)) break;
     if (iter >= D.iterations) { *status |= MYO_WORLD_SOLVER_MAXITER; break; }
     hessianFactor(slot, sm, t, ncon, nefc);
-    cholSolve(slot, sm + L.H, search, t);
+    cholSolve(slot, hessian(sm, L.H, nv, L.hshared), search, t);
     float sn = 0.f;
     TFOR(k, nv) { const float s = -search[k]; search[k] = s; sn = fmaf(s, s, sn); }
     sn = sqrtf(teamSum(t, sn));
@@ -1842,12 +1851,16 @@ __device__ __forceinline__ void forwardWorld(int slot, int fslot, SP sm, Tm t, W
 }
 
 // One warp = SCR_STRIDE worlds, TEAM lanes each; CTA_WARPS warps per CTA.  `scratch`: [nwarps][SmemLayout.total][SCR_STRIDE].
+// 14 warps, one CTA per SM: 8192 worlds x 8 lanes = 2048 warps = 147 CTAs, one wave on the 148 SMs with every SM
+// equally loaded (8-warp CTAs left 40 SMs with half the warps of the rest); <= 144 registers per thread.
 #ifndef CTA_WARPS
-#define CTA_WARPS 8
+#define CTA_WARPS 14
 #endif
 #ifndef CTA_MINBLOCKS
-#define CTA_MINBLOCKS 2   // <= 128 registers: two 8-warp CTAs per SM, so 8192 worlds x 8 lanes are resident in one wave
+#define CTA_MINBLOCKS 1
 #endif
+#define HSHARED_MAX_BYTES (200 * 1024)
+static inline size_t hessianTileBytes(int nv) { return (size_t)CTA_WARPS * SCR_STRIDE * nv * nv * sizeof(float); }
 __global__ void __launch_bounds__(32 * CTA_WARPS, CTA_MINBLOCKS) stepKernel(int slot, int nworld, int nsub, int forward_only, const int* __restrict__ mask,
                                                              int do_reset, float* __restrict__ scratch) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L; const FieldPtrs& F = tP[slot].F;
@@ -1984,12 +1997,21 @@ int VFN(myo_team_upload_)(int slot, const DevModel& D, const SmemLayout& L, cons
   if (slot < 0 || slot >= MYO_NSLOT) return -1;
   TParams& P = staging[slot];
   P.D = D; P.L = L; P.F = F;
+  P.L.hshared = hessianTileBytes(D.nv) <= HSHARED_MAX_BYTES ? 1 : 0;
   return cudaMemcpyToSymbolAsync(tP, &P, sizeof(TParams), (size_t)slot * sizeof(TParams), cudaMemcpyHostToDevice, (cudaStream_t)stream) == cudaSuccess ? 0 : -1;
 }
 int VFN(myo_team_launch_)(int slot, const SmemLayout& L, int nworld, int nsub, int forward_only, const int* reset_mask, int do_reset,
                           float* scratch, void* stream) {
   const int nwarp = (nworld + SCR_STRIDE - 1) / SCR_STRIDE;
-  stepKernel<<<(nwarp + CTA_WARPS - 1) / CTA_WARPS, 32 * CTA_WARPS, 0, (cudaStream_t)stream>>>(slot, nworld, nsub, forward_only, reset_mask, do_reset, scratch);
+  size_t shmem = hessianTileBytes(L.nv);
+  if (shmem > HSHARED_MAX_BYTES) shmem = 0;
+  static bool configured[64] = {false};   // per device: opt in to > 48 KB of dynamic shared memory once
+  int dev = 0;
+  if (shmem > 0 && cudaGetDevice(&dev) == cudaSuccess && dev >= 0 && dev < 64 && !configured[dev]) {
+    if (cudaFuncSetAttribute(stepKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)HSHARED_MAX_BYTES) != cudaSuccess) return -1;
+    configured[dev] = true;
+  }
+  stepKernel<<<(nwarp + CTA_WARPS - 1) / CTA_WARPS, 32 * CTA_WARPS, shmem, (cudaStream_t)stream>>>(slot, nworld, nsub, forward_only, reset_mask, do_reset, scratch);
   return cudaPeekAtLastError() == cudaSuccess ? 0 : -1;
 }
 // floats of scratch a batch of nworld worlds needs
