@@ -135,8 +135,8 @@ WORKLOAD = "MyoHand ({model}.xml, play.py:8) random-ctrl rollout, {nworld} world
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=200)
-    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=1000)
+    ap.add_argument("--warmup", type=int, default=100)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--model", default="hand")
     ap.add_argument("--nworld", type=int, default=8192, help="worlds per GPU")
@@ -222,11 +222,13 @@ def main():
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
-    t0 = time.perf_counter()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
     for _ in range(e2e_steps):
-        host_step()
+        host_step()          # H2D (pinned) -> step -> D2H, synchronises the stream
+    e1.record(stream)
     torch.cuda.synchronize()
-    e2e_ms = (time.perf_counter() - t0) * 1e3
+    e2e_ms = e0.elapsed_time(e1)
     te = torch.tensor([e2e_ms], device=dev)
     if world > 1:
         dist.all_reduce(te, op=dist.ReduceOp.MAX)
@@ -271,7 +273,7 @@ def main():
             "e2e": {"value": e2e_value, "unit": "env-steps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "api": "myo_step_host (C ABI, pinned host buffers)", "steps": e2e_steps},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
-                         "peak_source": peak_src, "kernel": "tpwKernel", "kernel_ms": kernel_ms,
+                         "peak_source": peak_src, "kernel": "stepKernel (team.cu, %d lanes per world)" % d.team, "kernel_ms": kernel_ms,
                          "algorithmic_bytes_per_launch": bytes_per_world * nw}}
     if not args.no_cpu:
         line["cpu_baseline"] = cpu_baseline(m, os.cpu_count() or 1)

@@ -184,6 +184,7 @@ void myo_batch_destroy(myo_batch* b) {
 int myo_batch_nconmax(const myo_batch* b) { return b ? b->D.nconmax : 0; }
 int myo_batch_njmax(const myo_batch* b) { return b ? b->D.njmax : 0; }
 int myo_batch_smem_bytes(const myo_batch* b) { return b ? b->L.total * 4 : 0; }
+int myo_batch_team(const myo_batch* b) { return b ? b->kern->team : 0; }
 int64_t myo_field_count(const myo_batch* b, int field) { return (b && field >= 0 && field < MYO_F_COUNT) ? fieldCount(b->D, field) : 0; }
 
 int myo_batch_bind(myo_batch* b, int field, void* dev_ptr, int64_t nbytes) {

@@ -49,6 +49,7 @@ def lib():
         L.myo_batch_nconmax.argtypes = [vp]
         L.myo_batch_njmax.argtypes = [vp]
         L.myo_batch_smem_bytes.argtypes = [vp]
+        L.myo_batch_team.argtypes = [vp]
         L.myo_field_count.restype = i64
         L.myo_field_count.argtypes = [vp, i32]
         L.myo_batch_bind.argtypes = [vp, i32, vp, i64]
@@ -67,5 +68,5 @@ def check(rc):
 
 
 EXPORTS = ["myo_model_create", "myo_model_destroy", "myo_batch_create", "myo_batch_destroy", "myo_batch_nconmax",
-           "myo_batch_njmax", "myo_batch_smem_bytes", "myo_field_count", "myo_field_itemsize", "myo_field_is_int", "myo_field_name", "myo_batch_bind",
+           "myo_batch_njmax", "myo_batch_smem_bytes", "myo_batch_team", "myo_field_count", "myo_field_itemsize", "myo_field_is_int", "myo_field_name", "myo_batch_bind",
            "myo_forward", "myo_step", "myo_reset", "myo_step_host", "myo_launch_count", "myo_last_error", "myo_kat_quat"]

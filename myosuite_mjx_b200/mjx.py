@@ -79,6 +79,7 @@ class Data:
         self.nconmax = L.myo_batch_nconmax(h)
         self.njmax = L.myo_batch_njmax(h)
         self.smem_bytes = L.myo_batch_smem_bytes(h)
+        self.team = L.myo_batch_team(h)
         self._t = {}
         dev = torch.device("cuda", model.device)
         if fields == "all":
@@ -140,6 +141,7 @@ class Data:
         h = ctypes.c_void_p()
         _lib.check(L.myo_batch_create(self.model._h, self.nworld, self.nconmax, self.njmax, ctypes.byref(h)))
         d._h, d.nconmax, d.njmax, d._t = h, self.nconmax, self.njmax, {}
+        d.smem_bytes, d.team = self.smem_bytes, self.team
         for k, v in self._t.items():
             d.bind(k, v.clone())
         return d
