@@ -64,6 +64,7 @@ struct DevModel {
   const float *body_off_mat, *body_imat, *geom_lmat, *site_lmat;   // 3x3 row-major rotations of the offsets above
   // ---- tendons
   const int *unit_tendon, *unit_type, *unit_s0, *unit_s1, *unit_geom, *unit_side, *unit_slot;
+  const int *unit_order;                       // [nunit] site-site units first, then the units that wrap a geom
   const float *unit_div, *unit_radius;
   const int *ten_ustart;                       // [nten+1]
   const int *ent_slot, *ent_dof, *ent_kind, *ent_unit;

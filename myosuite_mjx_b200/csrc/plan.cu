@@ -365,6 +365,14 @@ void myo_build_plan(const myo_model_desc& m, int nconmax_req, int njmax_req, Dev
   for (int i = 0; i < nv; i++) { col_start[i] = (int)col_nz.size(); for (int n = 0; n < nnz; n++) if (nz_d[n] == i) col_nz.push_back(n); }
   col_start[nv] = (int)col_nz.size();
   D.unit_tendon = upload(u_t, owned); D.unit_type = upload(u_type, owned); D.unit_s0 = upload(u_s0, owned); D.unit_s1 = upload(u_s1, owned);
+  {  // processing order: site-site units first, wrapping units last, so the lanes of a team run the wrap code together
+    std::vector<int> order;
+    for (size_t u = 0; u < u_g.size(); u++) if (u_g[u] < 0) order.push_back((int)u);
+    for (int ty : {(int)UNIT_SPHERE, (int)UNIT_CYLINDER})
+      for (size_t u = 0; u < u_g.size(); u++) if (u_g[u] >= 0 && u_type[u] == ty) order.push_back((int)u);
+    for (size_t u = 0; u < u_g.size(); u++) if (u_g[u] >= 0 && u_type[u] != UNIT_SPHERE && u_type[u] != UNIT_CYLINDER) order.push_back((int)u);
+    D.unit_order = upload(order, owned);
+  }
   D.unit_geom = upload(u_g, owned); D.unit_side = upload(u_side, owned); D.unit_slot = upload(u_slot, owned); D.unit_div = upload(u_div, owned);
   D.unit_radius = upload(u_rad, owned); D.ten_ustart = upload(ten_ustart, owned); D.ent_slot = upload(e_slot, owned); D.ent_dof = upload(e_dof, owned);
   D.ent_kind = upload(e_kind, owned); D.ent_unit = upload(e_unit, owned); D.ent_scale = upload(e_scale, owned); D.nz_estart = upload(nz_estart, owned);

@@ -574,7 +574,8 @@ __device__ __noinline__ float wrapGeom(f3 x0, f3 x1, f3 gpos, const float* gmat,
 // mj_tendon: path lengths + sparse moment arms
 __device__ __noinline__ void tendons(int slot, int fslot, SP sm, Tm t, World W) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L; const FieldPtrs& F = tP[fslot].F;
-  TFOR(u, D.nunit) {
+  TFOR(uo, D.nunit) {
+    const int u = D.unit_order[uo];
     const int s0 = D.unit_s0[u], s1 = D.unit_s1[u], g = D.unit_geom[u];
     const int f0 = D.site_frame[s0], f1 = D.site_frame[s1];
     const f3 p0 = ld3(FR_POS(sm, L, f0)) + mulM(FR_MAT(sm, L, f0), ld3(D.site_lpos + 3 * s0));
