@@ -157,7 +157,12 @@ struct Tm { int tl; unsigned mask; };
 #else
 #define TSYNC() __syncwarp(t.mask)
 #endif
-#define TFOR(i, n) _Pragma("unroll 1") for (int i = t.tl; i < (n); i += TEAM)
+#ifndef TFOR_UNROLL
+#define TFOR_UNROLL 1
+#endif
+#define TFOR_PRAGMA_(x) _Pragma(#x)
+#define TFOR_PRAGMA(n) TFOR_PRAGMA_(unroll n)
+#define TFOR(i, n) TFOR_PRAGMA(TFOR_UNROLL) for (int i = t.tl; i < (n); i += TEAM)
 __device__ __forceinline__ float teamSum(Tm t, float v) {
 #pragma unroll
   for (int o = TEAM / 2; o > 0; o >>= 1) v += __shfl_xor_sync(t.mask, v, o);
