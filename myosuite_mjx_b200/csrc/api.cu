@@ -27,6 +27,7 @@ struct myo_batch {
   int slot;      // constant-memory parameter slot
   const TeamVariant* kern;   // step kernel variant (lanes per world) chosen for this batch size
   bool dirty;    // parameters changed since the last upload
+  bool wide;     // some wide output field is bound: the output kernel runs after the step kernel
   float* scratch; // per-world intermediates, [nwarps][L.total][worlds per warp]
   std::vector<void*> owned;
 };
@@ -206,12 +207,25 @@ static int launch(myo_batch* b, int nsub, int forward_only, const int32_t* mask,
   int rc = checkReady(b);
   if (rc) return rc;
   if (b->dirty) {
-    if (b->kern->upload(b->slot, b->D, b->L, b->F, stream) != 0) return fail(MYO_ERR_CUDA, "parameter upload failed");
+    // wide outputs (out.cu) are written by the second kernel; the step kernel sees null pointers for them
+    static const bool wide_on = !(getenv("MYO_WIDE_OUT") && atoi(getenv("MYO_WIDE_OUT")) == 0);
+    FieldPtrs Fstep = b->F;
+    b->wide = false;
+    if (wide_on)
+      for (int i = 0; i < kNumWideOutFields; i++)
+        if (b->F.p[kWideOutFields[i]]) { Fstep.p[kWideOutFields[i]] = nullptr; b->wide = true; }
+    if (b->kern->upload(b->slot, b->D, b->L, Fstep, stream) != 0) return fail(MYO_ERR_CUDA, "parameter upload failed");
+    if (b->wide && myo_out_upload(b->slot, b->D, b->L, b->F, stream) != 0) return fail(MYO_ERR_CUDA, "parameter upload failed");
     b->dirty = false;
   }
   g_launches++;
   if (b->kern->launch(b->slot, b->L, b->nworld, nsub, forward_only, mask, do_reset, b->scratch, stream) != 0)
     return fail(MYO_ERR_CUDA, std::string("kernel launch failed: ") + cudaGetErrorString(cudaGetLastError()));
+  if (b->wide) {
+    g_launches++;
+    if (myo_out_launch(b->slot, b->nworld, 32 / b->kern->team, mask, do_reset, b->scratch, stream) != 0)
+      return fail(MYO_ERR_CUDA, std::string("kernel launch failed: ") + cudaGetErrorString(cudaGetLastError()));
+  }
   return MYO_OK;
 }
 int myo_forward(myo_batch* b, void* stream) { return launch(b, 0, 1, nullptr, 0, stream); }

@@ -112,6 +112,7 @@ struct SmemLayout {
   int qpos, qvel, act, ctrl, frames, xanchor, xaxis, rootcom, cinert, crb, cdof, cdof_dot, cvel, cacc, qM, qLD, qLDinv, qH,
       qHinv, tenlen, tenvel, tenJ, actlen, actvel, actforce, actdot, bias, passive, qfrc_act, smooth, qfrc_con, qacc_smooth,
       qacc, warm, tmpv, tforce;
+  int counts;    // ncon, nefc, solver_niter of the last forward pass (int bits), read by the wide-output kernel
   // overlay region A (tendon stage)
   int slots, ulen, uwrap, tmpbody;
   // overlay region B (collision / constraint / solver stage)

@@ -32,6 +32,11 @@ MYO_DECLARE_TEAM(2)
 MYO_DECLARE_TEAM(4)
 MYO_DECLARE_TEAM(8)
 MYO_DECLARE_TEAM(16)
+// out.cu: wide mjData outputs, one thread per (world, item), written after the step kernel from its scratch
+extern const int kWideOutFields[];
+extern const int kNumWideOutFields;
+int myo_out_upload(int slot, const DevModel& D, const SmemLayout& L, const FieldPtrs& F, void* stream);
+int myo_out_launch(int slot, int nworld, int stride, const int* reset_mask, int do_reset, const float* scratch, void* stream);
 int myo_launch_quat_kat(int n, const float* qa, const float* qb, float* prod, float* mat, float* rotated, void* stream);
 
 #endif

@@ -1852,6 +1852,7 @@ __device__ __forceinline__ void forwardWorld(int slot, int fslot, SP sm, Tm t, W
     }
     TSYNC();
   }
+  if (live && t.tl == 0) { sm[L.counts] = __int_as_float(ncon); sm[L.counts + 1] = __int_as_float(nefc); sm[L.counts + 2] = __int_as_float(niter); }
   PHASE_SYNC();
   *ncon_o = ncon; *nefc_o = nefc; *niter_o = niter;
 }
