@@ -11,6 +11,8 @@
 // run when this kernel is switched off with MYO_WIDE_OUT=0).
 #include <cuda_runtime.h>
 
+#include <cstdlib>
+
 #include "devmodel.h"
 #include "internal.h"
 
@@ -39,7 +41,7 @@ __device__ __forceinline__ void framePose(const Ctx& c, const SmemLayout& L, int
       for (int j = 0; j < 3; j++) M[3 * i + j] = fmaf(R[3 * i], lmat[j], fmaf(R[3 * i + 1], lmat[3 + j], R[3 * i + 2] * lmat[6 + j]));
 }
 
-__global__ void __launch_bounds__(128) outKernel(int slot, int nworld, int stride, const int* __restrict__ mask, int do_reset,
+__global__ void __launch_bounds__(128, 8) outKernel(int slot, int nworld, int stride, const int* __restrict__ mask, int do_reset,
                                                  const float* __restrict__ scratch) {
   const DevModel& D = oP[slot].D; const SmemLayout& L = oP[slot].L; const FieldPtrs& F = oP[slot].F;
   Ctx c; c.w = (size_t)blockIdx.x * 128 + threadIdx.x; c.nw = (size_t)nworld; c.stride = (size_t)stride;
@@ -170,8 +172,9 @@ int myo_out_upload(int slot, const DevModel& D, const SmemLayout& L, const Field
 }
 int myo_out_launch(int slot, int nworld, int stride, const int* reset_mask, int do_reset, const float* scratch, void* stream) {
   dim3 grid((nworld + 127) / 128, 1);
-  // enough item-chunks to give every SM several CTAs
-  const int want = 148 * 8;
+  // 8 CTAs are resident per SM (64 registers); many short CTAs (8 waves) let the hardware scheduler even out the item costs
+  static const int want_env = getenv("MYO_OUT_BLOCKS") ? atoi(getenv("MYO_OUT_BLOCKS")) : 0;   // developer knob
+  const int want = want_env > 0 ? want_env : 148 * 8 * 8;
   grid.y = (unsigned)((want + grid.x - 1) / grid.x);
   if (grid.y < 1) grid.y = 1;
   if (grid.y > 512) grid.y = 512;
