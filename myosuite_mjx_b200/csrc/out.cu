@@ -7,6 +7,7 @@
 //   ten_J, actuator_moment                                                      (mj_tendon / mj_transmission, dense rows)
 //   qM                                                                          (mj_crb, dense symmetric)
 //   efc_J                                                                       (mj_makeConstraint, dense rows)
+//   contact_* , efc_pos/margin/D/aref/force/type, xanchor, xaxis, cdof          (small per-row copies)
 // Same arithmetic, in the same order, as the step kernel's own writers for these fields (which remain in team.cu and
 // run when this kernel is switched off with MYO_WIDE_OUT=0).
 #include <cuda_runtime.h>
@@ -53,11 +54,22 @@ __global__ void __launch_bounds__(128, 8) outKernel(int slot, int nworld, int st
   void* xpos = F.p[MYO_F_XPOS]; void* xquat = F.p[MYO_F_XQUAT]; void* xmat = F.p[MYO_F_XMAT]; void* xipos = F.p[MYO_F_XIPOS];
   void* ximat = F.p[MYO_F_XIMAT]; void* tj = F.p[MYO_F_TEN_J]; void* am = F.p[MYO_F_ACTUATOR_MOMENT]; void* qMo = F.p[MYO_F_QM];
   void* eJ = F.p[MYO_F_EFC_J];
+  void* cg = F.p[MYO_F_CONTACT_GEOM]; void* cdim = F.p[MYO_F_CONTACT_DIM]; void* cadr = F.p[MYO_F_CONTACT_EFC_ADDRESS];
+  void* cdist = F.p[MYO_F_CONTACT_DIST]; void* cpos = F.p[MYO_F_CONTACT_POS]; void* cfr = F.p[MYO_F_CONTACT_FRAME];
+  void* cinc = F.p[MYO_F_CONTACT_INCLUDEMARGIN]; void* cfri = F.p[MYO_F_CONTACT_FRICTION]; void* csr = F.p[MYO_F_CONTACT_SOLREF];
+  void* csi = F.p[MYO_F_CONTACT_SOLIMP];
+  void* epos = F.p[MYO_F_EFC_POS]; void* emar = F.p[MYO_F_EFC_MARGIN]; void* eD = F.p[MYO_F_EFC_D]; void* earef = F.p[MYO_F_EFC_AREF];
+  void* efrc = F.p[MYO_F_EFC_FORCE]; void* etyp = F.p[MYO_F_EFC_TYPE];
+  void* xa = F.p[MYO_F_XANCHOR]; void* xx = F.p[MYO_F_XAXIS]; void* cdo = F.p[MYO_F_CDOF];
   const int n0 = (sp || smt) ? D.nsite : 0, n1 = n0 + ((gp || gm) ? D.ngeom : 0),
             n2 = n1 + ((xpos || xquat || xmat || xipos || ximat) ? D.nbody : 0), n3 = n2 + (tj ? D.nten : 0), n4 = n3 + (am ? D.nu : 0),
-            n5 = n4 + (qMo ? nv : 0), n6 = n5 + (eJ ? D.njmax : 0);
-  const int nefc = eJ ? __float_as_int(S(c, L.counts + 1)) : 0;   // left by the step kernel: ncon, nefc, niter
-  for (int it = blockIdx.y; it < n6; it += gridDim.y) {
+            n5 = n4 + (qMo ? nv : 0), n6 = n5 + (eJ ? D.njmax : 0),
+            n7 = n6 + ((cg || cdim || cadr || cdist || cpos || cfr || cinc || cfri || csr || csi) ? D.nconmax : 0),
+            n8 = n7 + ((epos || emar || eD || earef || efrc || etyp) ? D.njmax : 0), n9 = n8 + ((xa || xx) ? D.njnt : 0),
+            n10 = n9 + (cdo ? nv : 0);
+  const int ncon = __float_as_int(S(c, L.counts));
+  const int nefc = __float_as_int(S(c, L.counts + 1));   // left by the step kernel: ncon, nefc, niter
+  for (int it = blockIdx.y; it < n10; it += gridDim.y) {
     if (it < n0) {
       const int q = it;
       float p[3], M[9], R[9];
@@ -134,7 +146,7 @@ __global__ void __launch_bounds__(128, 8) outKernel(int slot, int nworld, int st
       const int a = D.dof_Madr[i], d = D.dof_rowlen[i];
       for (int q = 0; q < d; q++) OF(qMo, i * nv + D.M_col[a + q]) = S(c, L.qM + a + q);
       for (int e = D.desc_start[i]; e < D.desc_start[i + 1]; e++) OF(qMo, i * nv + D.desc_dof[e]) = S(c, L.qM + D.desc_idx[e]);
-    } else {                // dense efc_J row from the implied representation (see team.cu "constraints")
+    } else if (it < n6) {   // dense efc_J row from the implied representation (see team.cu "constraints")
       const int r = it - n5;
       const bool on = r < nefc;
       const int njm = D.njmax;
@@ -151,6 +163,55 @@ __global__ void __launch_bounds__(128, 8) outKernel(int slot, int nworld, int st
         }
         OF(eJ, r * nv + k) = v;
       }
+    } else if (it < n7) {   // contact record (padded to nconmax)
+      const int q = it - n6;
+      const bool on = q < ncon;
+      const int cr = L.con + 12 * q;
+      const int pr = on ? __float_as_int(S(c, cr + 7)) : 0;
+      const float* pp = D.pair_prm + 16 * pr;
+      if (cg) { ((int*)cg)[(size_t)(2 * q) * c.nw + c.w] = on ? D.cg_geom[D.pair_cg1[pr]] : -1; ((int*)cg)[(size_t)(2 * q + 1) * c.nw + c.w] = on ? D.cg_geom[D.pair_cg2[pr]] : -1; }
+      if (cdim) ((int*)cdim)[(size_t)q * c.nw + c.w] = on ? __float_as_int(S(c, cr + 9)) : 0;
+      if (cadr) ((int*)cadr)[(size_t)q * c.nw + c.w] = on ? __float_as_int(S(c, cr + 8)) : -1;
+      if (cdist) OF(cdist, q) = on ? S(c, cr) : 0.f;
+      if (cpos) for (int k = 0; k < 3; k++) OF(cpos, 3 * q + k) = on ? S(c, cr + 1 + k) : 0.f;
+      if (cfr) {
+        float n[3] = {0.f, 0.f, 0.f}, y[3] = {0.f, 0.f, 0.f}, z[3] = {0.f, 0.f, 0.f};
+        if (on) {   // contact frame: normal, then the tangent basis of team.cu makeFrame
+          for (int k = 0; k < 3; k++) n[k] = S(c, cr + 4 + k);
+          float t[3] = {0.f, 0.f, 0.f};
+          if (n[1] < 0.5f && n[1] > -0.5f) t[1] = 1.f; else t[2] = 1.f;
+          const float d = fmaf(n[0], t[0], fmaf(n[1], t[1], n[2] * t[2]));
+          for (int k = 0; k < 3; k++) t[k] -= n[k] * d;
+          const float nn = sqrtf(fmaf(t[0], t[0], fmaf(t[1], t[1], t[2] * t[2])));
+          if (nn < 1e-15f) { t[0] = 1.f; t[1] = 0.f; t[2] = 0.f; } else { const float s = 1.f / nn; t[0] *= s; t[1] *= s; t[2] *= s; }
+          y[0] = t[0]; y[1] = t[1]; y[2] = t[2];
+          z[0] = n[1] * t[2] - n[2] * t[1]; z[1] = n[2] * t[0] - n[0] * t[2]; z[2] = n[0] * t[1] - n[1] * t[0];
+        }
+        for (int k = 0; k < 3; k++) { OF(cfr, 9 * q + k) = n[k]; OF(cfr, 9 * q + 3 + k) = y[k]; OF(cfr, 9 * q + 6 + k) = z[k]; }
+      }
+      if (cinc) OF(cinc, q) = on ? pp[0] - pp[1] : 0.f;
+      if (cfri) for (int k = 0; k < 5; k++) OF(cfri, 5 * q + k) = on ? pp[2 + k] : 0.f;
+      if (csr) for (int k = 0; k < 2; k++) OF(csr, 2 * q + k) = on ? pp[7 + k] : 0.f;
+      if (csi) for (int k = 0; k < 5; k++) OF(csi, 5 * q + k) = on ? pp[9 + k] : 0.f;
+    } else if (it < n8) {   // per-row constraint scalars (padded to njmax)
+      const int r = it - n7, njm = D.njmax;
+      const bool on = r < nefc;
+      if (epos) OF(epos, r) = on ? S(c, L.efc + E_POS * njm + r) : 0.f;
+      if (emar) OF(emar, r) = on ? S(c, L.efc + E_MARGIN * njm + r) : 0.f;
+      if (eD) OF(eD, r) = on ? S(c, L.efc + E_D * njm + r) : 0.f;
+      if (earef) OF(earef, r) = on ? S(c, L.efc + E_AREF * njm + r) : 0.f;
+      if (efrc) OF(efrc, r) = on ? S(c, L.efc + E_FORCE * njm + r) : 0.f;
+      if (etyp) {
+        const int d0 = on ? __float_as_int(S(c, L.efc + E_DESC0 * njm + r)) : 0, type = d0 & 3;
+        ((int*)etyp)[(size_t)r * c.nw + c.w] = !on ? -1 : (type == ROW_EQ ? 0 : (type == ROW_LIMJ ? 3 : (type == ROW_LIMT ? 4 : (__float_as_int(S(c, L.efc + E_DESC1 * njm + r)) < 0 ? 5 : 6))));
+      }
+    } else if (it < n9) {
+      const int j = it - n8;
+      if (xa) for (int k = 0; k < 3; k++) OF(xa, 3 * j + k) = S(c, L.xanchor + 3 * j + k);
+      if (xx) for (int k = 0; k < 3; k++) OF(xx, 3 * j + k) = S(c, L.xaxis + 3 * j + k);
+    } else {
+      const int i = it - n9;
+      for (int k = 0; k < 6; k++) OF(cdo, 6 * i + k) = S(c, L.cdof + 6 * i + k);
     }
   }
 }
@@ -158,7 +219,11 @@ __global__ void __launch_bounds__(128, 8) outKernel(int slot, int nworld, int st
 
 // fields this kernel writes (the step kernel is given null pointers for them when the wide path is on)
 const int kWideOutFields[] = {MYO_F_SITE_XPOS, MYO_F_SITE_XMAT, MYO_F_GEOM_XPOS, MYO_F_GEOM_XMAT, MYO_F_XPOS, MYO_F_XQUAT, MYO_F_XMAT,
-                              MYO_F_XIPOS, MYO_F_XIMAT, MYO_F_TEN_J, MYO_F_ACTUATOR_MOMENT, MYO_F_QM, MYO_F_EFC_J};
+                              MYO_F_XIPOS, MYO_F_XIMAT, MYO_F_TEN_J, MYO_F_ACTUATOR_MOMENT, MYO_F_QM, MYO_F_EFC_J,
+                              MYO_F_CONTACT_GEOM, MYO_F_CONTACT_DIM, MYO_F_CONTACT_EFC_ADDRESS, MYO_F_CONTACT_DIST, MYO_F_CONTACT_POS,
+                              MYO_F_CONTACT_FRAME, MYO_F_CONTACT_INCLUDEMARGIN, MYO_F_CONTACT_FRICTION, MYO_F_CONTACT_SOLREF,
+                              MYO_F_CONTACT_SOLIMP, MYO_F_EFC_POS, MYO_F_EFC_MARGIN, MYO_F_EFC_D, MYO_F_EFC_AREF, MYO_F_EFC_FORCE,
+                              MYO_F_EFC_TYPE, MYO_F_XANCHOR, MYO_F_XAXIS, MYO_F_CDOF};
 const int kNumWideOutFields = sizeof(kWideOutFields) / sizeof(int);
 
 int myo_out_upload(int slot, const DevModel& D, const SmemLayout& L, const FieldPtrs& F, void* stream) {
