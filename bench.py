@@ -273,7 +273,8 @@ def main():
             "e2e": {"value": e2e_value, "unit": "env-steps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "api": "myo_step_host (C ABI, pinned host buffers)", "steps": e2e_steps},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
-                         "peak_source": peak_src, "kernel": "stepKernel (team.cu, %d lanes per world)" % d.team, "kernel_ms": kernel_ms,
+                         "peak_source": peak_src, "kernel": ("stepKernel (team.cu, %d lanes per world) + outKernel (out.cu): one myo_step" if args.fields == "all" else "stepKernel (team.cu, %d lanes per world)") % d.team,
+                         "kernel_ms": kernel_ms,
                          "algorithmic_bytes_per_launch": bytes_per_world * nw}}
     if not args.no_cpu:
         line["cpu_baseline"] = cpu_baseline(m, os.cpu_count() or 1)

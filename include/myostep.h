@@ -218,6 +218,72 @@ int myo_reset(myo_batch *b, const int32_t *world_mask_dev, void *cuda_stream);
 int myo_step_host(myo_batch *b, int nsubsteps, const float *qpos, const float *qvel, const float *act,
                   const float *ctrl, float *qpos_out, float *qvel_out, float *act_out, void *cuda_stream);
 
+/* ------------------------------------------------------------------------------------------------------------------
+ * Fused env layer (SURVEY 8f rows n1 + n3): the elementwise work either side of the physics step of the reference's
+ * pose environments, as two small kernels around myo_step -- no host round trip per env step.
+ *   pre  : action -> ctrl      BaseV0.step, myosuite/envs/myo/base_v0.py:81-110 (muscle squash 1/(1+exp(-5(a-.5))),
+ *                               fatigue 3CC-r, reafferentation EIP->EPL) and Robot.process_actuator "default_robot"
+ *                               normalisation, myosuite/robot/robot.py:771-783
+ *          fatigue              CumulativeFatigue.compute_act, myosuite/envs/myo/fatigue.py:61-108
+ *   step : frame_skip x mj_step with ctrl held   myosuite/robot/robot.py:880-882
+ *   post : obs / reward terms / done             PoseEnvV0.get_obs_dict / get_reward_dict,
+ *                                                myosuite/envs/myo/myobase/pose_v0.py:98-138
+ *          masked auto-reset with target resampling   PoseEnvV0.reset / get_target_pose, pose_v0.py:141-168,190-251
+ * Random draws are a counter-based hash of (seed, global world index, episode, stream, index), so a world's episode
+ * sequence does not depend on the batch size or on the number of GPUs.  All env buffers are caller-owned device
+ * memory in the [k][nworld] layout, bound with myo_env_bind. */
+enum { MYO_COND_NONE = 0, MYO_COND_SARCOPENIA = 1, MYO_COND_FATIGUE = 2, MYO_COND_REAFFERENTATION = 3 };
+enum { MYO_OBS_TIME = 0, MYO_OBS_QPOS = 1, MYO_OBS_QVEL = 2, MYO_OBS_ACT = 3, MYO_OBS_POSE_ERR = 4 };   /* obs_dict keys */
+enum { MYO_TARGET_FIXED = 0, MYO_TARGET_GENERATE = 1 };
+enum { MYO_RESET_INIT = 0, MYO_RESET_RANDOM = 1 };
+enum { MYO_RWD_POSE = 0, MYO_RWD_BONUS, MYO_RWD_PENALTY, MYO_RWD_ACT_REG, MYO_RWD_SPARSE, MYO_RWD_SOLVED, MYO_RWD_COUNT };
+
+typedef enum myo_env_field {
+  MYO_E_ACTION = 0,   /* [nu]            input of myo_env_step */
+  MYO_E_OBS,          /* [nobs]          concatenation of the obs_keys entries, in order */
+  MYO_E_REWARD,       /* [1]             rwd_dict["dense"] */
+  MYO_E_DONE,         /* [1]             1.0 where the episode ended on this step (done or horizon) */
+  MYO_E_RWD_TERMS,    /* [MYO_RWD_COUNT] pose, bonus, penalty, act_reg, sparse, solved */
+  MYO_E_TARGET,       /* [ntarget]       target_jnt_value per world */
+  MYO_E_FATIGUE,      /* [3, nmuscle]    MA, MR, MF (only with MYO_COND_FATIGUE) */
+  MYO_E_STEPS,        /* [1] int32       env steps since the world's last reset */
+  MYO_E_EPISODE,      /* [1] int32       episodes started by the world (the RNG counter) */
+  MYO_E_COUNT
+} myo_env_field;
+
+/* host arrays; copied at myo_env_create */
+typedef struct myo_env_desc {
+  int32_t frame_skip, normalize_act, muscle_condition, epl_id, eip_id;
+  int32_t nobs_keys, obs_keys[8];
+  int32_t ntarget, target_type, reset_type, auto_reset, horizon, world_offset;
+  uint64_t seed;
+  float pose_thd, far_th, w_pose, w_bonus, w_act_reg, w_penalty;
+  float fatigue_F, fatigue_R, fatigue_r;
+  const int32_t *target_qposadr;   /* [ntarget] */
+  const float *target_range;       /* [ntarget,2] (generate) */
+  const float *target_value;       /* [ntarget]   (fixed) */
+  const float *init_qpos, *init_qvel;        /* [nq], [nv] */
+  const float *reset_lo, *reset_hi;          /* [nq] uniform reset range (jnt_range) */
+  const int32_t *act_is_muscle;              /* [nu] actuator_dyntype == mjDYN_MUSCLE */
+  const float *ctrl_lo, *ctrl_hi;            /* [nu] actuator_ctrlrange */
+  const float *tau_act, *tau_deact;          /* [nu] actuator_dynprm[:,0], [:,1] */
+} myo_env_desc;
+
+typedef struct myo_env myo_env;
+int myo_env_create(myo_batch *b, const myo_env_desc *desc, myo_env **out);
+void myo_env_destroy(myo_env *e);
+int64_t myo_env_field_count(const myo_env *e, int field);   /* elements per world */
+int myo_env_bind(myo_env *e, int field, void *dev_ptr, int64_t nbytes);
+int myo_env_seed(myo_env *e, uint64_t seed);
+/* reset the masked worlds (NULL = all): new target, new initial state, zero reward / done, fresh observation.
+ * Derived mjData fields are refreshed by the next step (call myo_forward for them earlier). */
+int myo_env_reset(myo_env *e, const int32_t *world_mask_dev, void *cuda_stream);
+/* one env step of every world: pre kernel, frame_skip fused mj_steps, post kernel (3 or 4 launches, no sync) */
+int myo_env_step(myo_env *e, void *cuda_stream);
+/* MujocoEnv.forward (obs + reward terms + done from the CURRENT state; no physics, no counters, no reset):
+ * what the reference evaluates after reset and after every step (myosuite/envs/myo/base_v0.py:120). */
+int myo_env_forward(myo_env *e, void *cuda_stream);
+
 /* Known-answer hook for the device rotation helpers used by kinematics and free-joint integration (reference KATs:
  * myosuite/tests/mjx/test_quat_math.py against myosuite/utils/quat_math.py:15 mulQuat, :160 quat2mat, :209 rotVecQuat).
  * Device pointers: qa, qb [n,4] (w,x,y,z); prod [n,4] = qa*qb; mat [n,9] = quat2mat(normalise(qa));

@@ -12,26 +12,6 @@
 #include "internal.h"
 
 
-struct myo_model {
-  DevModel D;
-  SmemLayout L;
-  std::vector<void*> owned;
-  int device;
-};
-struct myo_batch {
-  const myo_model* model;
-  DevModel D;   // copy with this batch's nconmax / njmax
-  SmemLayout L;
-  FieldPtrs F;
-  int nworld;
-  int slot;      // constant-memory parameter slot
-  const TeamVariant* kern;   // step kernel variant (lanes per world) chosen for this batch size
-  bool dirty;    // parameters changed since the last upload
-  bool wide;     // some wide output field is bound: the output kernel runs after the step kernel
-  float* scratch; // per-world intermediates, [nwarps][L.total][worlds per warp]
-  std::vector<void*> owned;
-};
-
 namespace {
 const TeamVariant kVariants[] = {
     {1, myo_team_upload_1, myo_team_launch_1, myo_team_scratch_1}, {2, myo_team_upload_2, myo_team_launch_2, myo_team_scratch_2},
@@ -49,6 +29,10 @@ const TeamVariant* pickVariant(int nworld) {
 thread_local std::string g_err;
 bool g_slot_used[64] = {false};
 int fail(int code, const std::string& msg) { g_err = msg; return code; }
+}  // namespace
+int myo_fail(int code, const std::string& msg) { return fail(code, msg); }
+void myo_count_launch(int n) { g_launches += n; }
+namespace {
 
 const char* kFieldNames[MYO_F_COUNT] = {
     "qpos", "qvel", "act", "ctrl", "time", "qacc_warmstart", "qacc", "qacc_smooth", "act_dot", "xpos", "xquat", "xmat", "xipos",

@@ -1,0 +1,335 @@
+// Fused env layer around the physics step (include/myostep.h "Fused env layer"; SURVEY 8f rows n1 + n3).
+// Reference behaviour restated here (formulas, not code):
+//   action -> ctrl            myosuite/envs/myo/base_v0.py:81-110, myosuite/robot/robot.py:771-783
+//   fatigue (3CC-r)           myosuite/envs/myo/fatigue.py:61-108
+//   obs / reward terms / done myosuite/envs/myo/myobase/pose_v0.py:98-138
+//   reset, target sampling    myosuite/envs/myo/myobase/pose_v0.py:141-168,190-251
+// Layout: every env buffer is [k][nworld] with the world axis fastest, like the mjData fields, so the lanes of a warp
+// (32 consecutive worlds) read and write one full line per element.  All arithmetic is float32.
+#include <cuda_runtime.h>
+
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "devmodel.h"
+#include "internal.h"
+
+struct EnvTables {   // device copies of the myo_env_desc arrays
+  const int* target_qposadr; const float *target_range, *target_value, *init_qpos, *init_qvel, *reset_lo, *reset_hi;
+  const int* act_is_muscle; const int* muscle_slot;   // muscle_slot[a]: index among the muscle actuators, -1 otherwise
+  const float *ctrl_lo, *ctrl_hi, *tau_act, *tau_deact;
+};
+struct EnvParams {
+  int nworld, nq, nv, na, nu, nmuscle;
+  int frame_skip, normalize_act, cond, epl, eip;
+  int nobs_keys, obs_keys[8], nobs;
+  int ntarget, target_type, reset_type, auto_reset, horizon, world_offset;
+  unsigned long long seed;
+  float dt, pose_thd, far_th, w_pose, w_bonus, w_act_reg, w_penalty, fat_F, fat_R, fat_r;
+  EnvTables T;
+  void* E[MYO_E_COUNT];   // env buffers
+  float *qpos, *qvel, *act, *ctrl, *time, *warm; int* status;   // bound state fields of the batch
+};
+
+struct myo_env {
+  myo_batch* b;
+  EnvParams P;
+  std::vector<void*> owned;
+};
+
+namespace {
+// counter-based uniform in [0, 1): splitmix64 finaliser of a key built from (seed, world, episode, stream, index)
+__host__ __device__ inline float envUniform(unsigned long long seed, unsigned gworld, unsigned episode, unsigned stream, unsigned idx) {
+  unsigned long long z = seed ^ ((unsigned long long)gworld * 0xD1B54A32D192ED03ull) ^ ((unsigned long long)episode * 0x8CB92BA72F3D8DD7ull) ^
+                         ((((unsigned long long)stream << 32) | idx) * 0x9E3779B97F4A7C15ull);
+  z += 0x9E3779B97F4A7C15ull;
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+  z ^= z >> 31;
+  return (float)(z >> 40) * (1.0f / 16777216.0f);
+}
+
+#define EF(field, k) ((float*)P.E[field])[(size_t)(k) * nw + w]
+#define EI(field, k) ((int*)P.E[field])[(size_t)(k) * nw + w]
+#define ST(ptr, k) (ptr)[(size_t)(k) * nw + w]
+
+// ---- pre: action -> ctrl, one thread per (actuator, world)
+__global__ void __launch_bounds__(256) envPreKernel(const EnvParams P) {
+  const size_t nw = (size_t)P.nworld;
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= nw * (size_t)P.nu) return;
+  const int a = (int)(i / nw);
+  const size_t w = i - (size_t)a * nw;
+  const bool muscle = P.T.act_is_muscle[a] != 0;
+  const bool squash = P.na > 0 && P.normalize_act;   // base_v0.py:85: only then are muscle entries squashed
+  int src = a;
+  bool zero = false;
+  if (P.cond == MYO_COND_REAFFERENTATION) {          // base_v0.py:104-108: EPL takes EIP's command, EIP is silenced
+    if (a == P.epl) src = P.eip;
+    else if (a == P.eip) zero = true;
+  }
+  float x = EF(MYO_E_ACTION, src);
+  if (squash) {
+    if (P.T.act_is_muscle[src]) x = 1.0f / (1.0f + expf(-5.0f * (x - 0.5f)));
+  } else if (P.normalize_act) {                       // robot.py:771-783 (default_robot, "pos"): mean + a * range / 2
+    x = 0.5f * (P.T.ctrl_lo[src] + P.T.ctrl_hi[src]) + x * (0.5f * (P.T.ctrl_hi[src] - P.T.ctrl_lo[src]));
+  }
+  if (zero) x = 0.f;
+  if (P.cond == MYO_COND_FATIGUE && muscle) {         // fatigue.py:61-108, target load TL = x
+    const int m = P.T.muscle_slot[a], nm = P.nmuscle;
+    float MA = EF(MYO_E_FATIGUE, m), MR = EF(MYO_E_FATIGUE, nm + m), MF = EF(MYO_E_FATIGUE, 2 * nm + m);
+    const float TL = x, dt = P.dt, F = P.fat_F;
+    const float LD = 1.0f / P.T.tau_act[a] * (0.5f + 1.5f * MA), LR = (0.5f + 1.5f * MA) / P.T.tau_deact[a];
+    float C, rR;
+    if (MA < TL) { C = MR > TL - MA ? LD * (TL - MA) : LD * MR; rR = P.fat_R; }
+    else { C = LR * (TL - MA); rR = P.fat_r * P.fat_R; }
+    const float lo = fmaxf(-MA / dt + F * MA, (MR - 1.0f) / dt + rR * MF);
+    const float hi = fminf((1.0f - MA) / dt + F * MA, MR / dt + rR * MF);
+    C = fminf(fmaxf(C, lo), hi);                      // np.clip(C, lo, hi)
+    const float dMA = (C - F * MA) * dt, dMR = (-C + rR * MF) * dt, dMF = (F * MA - rR * MF) * dt;
+    MA += dMA; MR += dMR; MF += dMF;
+    EF(MYO_E_FATIGUE, m) = MA; EF(MYO_E_FATIGUE, nm + m) = MR; EF(MYO_E_FATIGUE, 2 * nm + m) = MF;
+    x = MA;
+  }
+  ST(P.ctrl, a) = x;
+}
+
+// new episode for world w: target, initial state, counters (pose_v0.py:190-251; robot.py:976-979 for the state write)
+__device__ void envResetWorld(const EnvParams& P, size_t w) {
+  const size_t nw = (size_t)P.nworld;
+  const unsigned gw = (unsigned)(P.world_offset + (int)w);
+  const unsigned ep = (unsigned)EI(MYO_E_EPISODE, 0);
+  for (int k = 0; k < P.ntarget; k++) {
+    float t;
+    if (P.target_type == MYO_TARGET_GENERATE) {
+      const float lo = P.T.target_range[2 * k], hi = P.T.target_range[2 * k + 1];
+      t = __fadd_rn(lo, __fmul_rn(hi - lo, envUniform(P.seed, gw, ep, 0u, (unsigned)k)));   // no fma: bit-equal to numpy float32
+    } else t = P.T.target_value[k];
+    EF(MYO_E_TARGET, k) = t;
+  }
+  for (int j = 0; j < P.nq; j++) {
+    float q = P.T.init_qpos[j];
+    if (P.reset_type == MYO_RESET_RANDOM) {
+      const float lo = P.T.reset_lo[j], hi = P.T.reset_hi[j];
+      q = __fadd_rn(lo, __fmul_rn(hi - lo, envUniform(P.seed, gw, ep, 1u, (unsigned)j)));
+    }
+    ST(P.qpos, j) = q;
+  }
+  for (int j = 0; j < P.nv; j++) { ST(P.qvel, j) = P.T.init_qvel[j]; ST(P.warm, j) = 0.f; }
+  for (int j = 0; j < P.na; j++) ST(P.act, j) = 0.f;
+  for (int j = 0; j < P.nu; j++) ST(P.ctrl, j) = 0.f;
+  ST(P.time, 0) = 0.f;
+  if (P.status) ST(P.status, 0) = 0;
+  if (P.cond == MYO_COND_FATIGUE)
+    for (int m = 0; m < P.nmuscle; m++) { EF(MYO_E_FATIGUE, m) = 0.f; EF(MYO_E_FATIGUE, P.nmuscle + m) = 1.f; EF(MYO_E_FATIGUE, 2 * P.nmuscle + m) = 0.f; }
+  EI(MYO_E_STEPS, 0) = 0;
+  EI(MYO_E_EPISODE, 0) = (int)(ep + 1u);
+}
+
+// obs vector from the state (pose_v0.py:98-116): concatenation of the obs_keys entries
+__device__ void envWriteObs(const EnvParams& P, size_t w) {
+  const size_t nw = (size_t)P.nworld;
+  int o = 0;
+  for (int q = 0; q < P.nobs_keys; q++) {
+    switch (P.obs_keys[q]) {
+      case MYO_OBS_TIME: EF(MYO_E_OBS, o++) = ST(P.time, 0); break;
+      case MYO_OBS_QPOS: for (int j = 0; j < P.nq; j++) EF(MYO_E_OBS, o++) = ST(P.qpos, j); break;
+      case MYO_OBS_QVEL: for (int j = 0; j < P.nv; j++) EF(MYO_E_OBS, o++) = ST(P.qvel, j) * P.dt; break;
+      case MYO_OBS_ACT:
+        if (P.na > 0) { for (int j = 0; j < P.na; j++) EF(MYO_E_OBS, o++) = ST(P.act, j); }
+        else { for (int j = 0; j < P.nq; j++) EF(MYO_E_OBS, o++) = 0.f; }   // pose_v0.py:108-112: zeros_like(qpos)
+        break;
+      case MYO_OBS_POSE_ERR: for (int k = 0; k < P.ntarget; k++) EF(MYO_E_OBS, o++) = EF(MYO_E_TARGET, k) - ST(P.qpos, P.T.target_qposadr[k]); break;
+    }
+  }
+}
+
+// ---- post: reward terms, done, auto-reset, obs; one thread per world
+__global__ void __launch_bounds__(128) envPostKernel(const EnvParams P, const int advance) {
+  const size_t nw = (size_t)P.nworld;
+  const size_t w = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (w >= nw) return;
+  float d2 = 0.f;
+  for (int k = 0; k < P.ntarget; k++) { const float e = EF(MYO_E_TARGET, k) - ST(P.qpos, P.T.target_qposadr[k]); d2 = fmaf(e, e, d2); }
+  const float dist = sqrtf(d2);
+  float a2 = 0.f;
+  for (int j = 0; j < P.na; j++) { const float a = ST(P.act, j); a2 = fmaf(a, a, a2); }
+  float act_mag = sqrtf(a2);
+  if (P.na != 0) act_mag = act_mag / (float)P.na;
+  const float pose = -dist, bonus = (dist < P.pose_thd ? 1.f : 0.f) + (dist < 1.5f * P.pose_thd ? 1.f : 0.f);
+  const float penalty = dist > P.far_th ? -1.f : 0.f, act_reg = -act_mag;
+  const bool done = dist > P.far_th;
+  EF(MYO_E_RWD_TERMS, MYO_RWD_POSE) = pose; EF(MYO_E_RWD_TERMS, MYO_RWD_BONUS) = bonus; EF(MYO_E_RWD_TERMS, MYO_RWD_PENALTY) = penalty;
+  EF(MYO_E_RWD_TERMS, MYO_RWD_ACT_REG) = act_reg; EF(MYO_E_RWD_TERMS, MYO_RWD_SPARSE) = -dist;
+  EF(MYO_E_RWD_TERMS, MYO_RWD_SOLVED) = dist < P.pose_thd ? 1.f : 0.f;
+  // dense = sum over rwd_keys_wt in its dict order: pose, bonus, act_reg, penalty (pose_v0.py:16-21,134-136)
+  EF(MYO_E_REWARD, 0) = ((P.w_pose * pose + P.w_bonus * bonus) + P.w_act_reg * act_reg) + P.w_penalty * penalty;
+  const int steps = EI(MYO_E_STEPS, 0) + advance;
+  if (advance) EI(MYO_E_STEPS, 0) = steps;
+  const bool ended = done || (P.horizon > 0 && steps >= P.horizon);
+  EF(MYO_E_DONE, 0) = ended ? 1.f : 0.f;
+  if (ended && advance && P.auto_reset) envResetWorld(P, w);
+  envWriteObs(P, w);
+}
+
+__global__ void __launch_bounds__(128) envResetKernel(const EnvParams P, const int* __restrict__ mask) {
+  const size_t nw = (size_t)P.nworld;
+  const size_t w = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (w >= nw) return;
+  if (mask && !mask[w]) return;
+  envResetWorld(P, w);
+  EF(MYO_E_REWARD, 0) = 0.f; EF(MYO_E_DONE, 0) = 0.f;
+  for (int k = 0; k < MYO_RWD_COUNT; k++) EF(MYO_E_RWD_TERMS, k) = 0.f;
+  envWriteObs(P, w);
+}
+
+template <class T> const T* toDevice(const T* host, size_t n, std::vector<void*>& owned) {
+  if (!host || n == 0) return nullptr;
+  void* p = nullptr;
+  if (cudaMalloc(&p, n * sizeof(T)) != cudaSuccess) throw std::string("cudaMalloc failed");
+  if (cudaMemcpy(p, host, n * sizeof(T), cudaMemcpyHostToDevice) != cudaSuccess) { cudaFree(p); throw std::string("cudaMemcpy failed"); }
+  owned.push_back(p);
+  return (const T*)p;
+}
+int64_t envFieldCount(const EnvParams& P, int field) {
+  switch (field) {
+    case MYO_E_ACTION: return P.nu;
+    case MYO_E_OBS: return P.nobs;
+    case MYO_E_REWARD: case MYO_E_DONE: case MYO_E_STEPS: case MYO_E_EPISODE: return 1;
+    case MYO_E_RWD_TERMS: return MYO_RWD_COUNT;
+    case MYO_E_TARGET: return P.ntarget;
+    case MYO_E_FATIGUE: return P.cond == MYO_COND_FATIGUE ? 3 * P.nmuscle : 0;
+  }
+  return 0;
+}
+}  // namespace
+
+extern "C" {
+
+int myo_env_create(myo_batch* b, const myo_env_desc* d, myo_env** out) {
+  if (!b || !d || !out) return myo_fail(MYO_ERR_ARG, "bad argument");
+  const DevModel& D = b->D;
+  if (d->frame_skip < 1) return myo_fail(MYO_ERR_ARG, "frame_skip must be >= 1");
+  if (d->nobs_keys < 0 || d->nobs_keys > 8) return myo_fail(MYO_ERR_ARG, "at most 8 obs keys");
+  if (d->ntarget < 0 || (d->ntarget > 0 && !d->target_qposadr)) return myo_fail(MYO_ERR_ARG, "target_qposadr missing");
+  if (d->target_type == MYO_TARGET_GENERATE && d->ntarget > 0 && !d->target_range) return myo_fail(MYO_ERR_ARG, "target_range missing");
+  if (d->target_type == MYO_TARGET_FIXED && d->ntarget > 0 && !d->target_value) return myo_fail(MYO_ERR_ARG, "target_value missing");
+  if (!d->init_qpos || !d->init_qvel) return myo_fail(MYO_ERR_ARG, "init_qpos / init_qvel missing");
+  if (d->reset_type == MYO_RESET_RANDOM && (!d->reset_lo || !d->reset_hi)) return myo_fail(MYO_ERR_ARG, "reset range missing");
+  if (D.nu > 0 && (!d->act_is_muscle || !d->ctrl_lo || !d->ctrl_hi)) return myo_fail(MYO_ERR_ARG, "actuator tables missing");
+  if (d->muscle_condition == MYO_COND_FATIGUE && (!d->tau_act || !d->tau_deact)) return myo_fail(MYO_ERR_ARG, "tau_act / tau_deact missing");
+  if (d->muscle_condition == MYO_COND_REAFFERENTATION && (d->epl_id < 0 || d->epl_id >= D.nu || d->eip_id < 0 || d->eip_id >= D.nu))
+    return myo_fail(MYO_ERR_ARG, "reafferentation needs the EPL and EIP actuator ids");
+  for (int k = 0; k < d->ntarget; k++) if (d->target_qposadr[k] < 0 || d->target_qposadr[k] >= D.nq) return myo_fail(MYO_ERR_ARG, "target_qposadr out of range");
+  if (cudaSetDevice(b->model->device) != cudaSuccess) return myo_fail(MYO_ERR_CUDA, "cudaSetDevice failed: libmyostep has no CPU fallback");
+  myo_env* e = new myo_env();
+  e->b = b;
+  EnvParams& P = e->P;
+  memset(&P, 0, sizeof(P));
+  P.nworld = b->nworld; P.nq = D.nq; P.nv = D.nv; P.na = D.na; P.nu = D.nu;
+  P.frame_skip = d->frame_skip; P.normalize_act = d->normalize_act; P.cond = d->muscle_condition; P.epl = d->epl_id; P.eip = d->eip_id;
+  P.nobs_keys = d->nobs_keys;
+  P.ntarget = d->ntarget; P.target_type = d->target_type; P.reset_type = d->reset_type; P.auto_reset = d->auto_reset; P.horizon = d->horizon;
+  P.world_offset = d->world_offset; P.seed = d->seed;
+  P.dt = D.timestep * (float)d->frame_skip;
+  P.pose_thd = d->pose_thd; P.far_th = d->far_th; P.w_pose = d->w_pose; P.w_bonus = d->w_bonus; P.w_act_reg = d->w_act_reg; P.w_penalty = d->w_penalty;
+  P.fat_F = d->fatigue_F; P.fat_R = d->fatigue_R; P.fat_r = d->fatigue_r;
+  for (int q = 0; q < d->nobs_keys; q++) {
+    const int key = d->obs_keys[q];
+    P.obs_keys[q] = key;
+    switch (key) {
+      case MYO_OBS_TIME: P.nobs += 1; break;
+      case MYO_OBS_QPOS: P.nobs += D.nq; break;
+      case MYO_OBS_QVEL: P.nobs += D.nv; break;
+      case MYO_OBS_ACT: P.nobs += D.na > 0 ? D.na : D.nq; break;
+      case MYO_OBS_POSE_ERR: P.nobs += d->ntarget; break;
+      default: delete e; return myo_fail(MYO_ERR_ARG, "unknown obs key");
+    }
+  }
+  std::vector<int> slot(D.nu > 0 ? D.nu : 1, -1);
+  for (int a = 0; a < D.nu; a++) if (d->act_is_muscle[a]) slot[a] = P.nmuscle++;
+  try {
+    P.T.target_qposadr = toDevice(d->target_qposadr, d->ntarget, e->owned);
+    P.T.target_range = toDevice(d->target_range, 2 * (size_t)d->ntarget, e->owned);
+    P.T.target_value = toDevice(d->target_value, d->ntarget, e->owned);
+    P.T.init_qpos = toDevice(d->init_qpos, D.nq, e->owned);
+    P.T.init_qvel = toDevice(d->init_qvel, D.nv, e->owned);
+    P.T.reset_lo = toDevice(d->reset_lo, D.nq, e->owned);
+    P.T.reset_hi = toDevice(d->reset_hi, D.nq, e->owned);
+    P.T.act_is_muscle = toDevice(d->act_is_muscle, D.nu, e->owned);
+    P.T.muscle_slot = toDevice(slot.data(), D.nu, e->owned);
+    P.T.ctrl_lo = toDevice(d->ctrl_lo, D.nu, e->owned);
+    P.T.ctrl_hi = toDevice(d->ctrl_hi, D.nu, e->owned);
+    P.T.tau_act = toDevice(d->tau_act, D.nu, e->owned);
+    P.T.tau_deact = toDevice(d->tau_deact, D.nu, e->owned);
+  } catch (const std::string& msg) { myo_env_destroy(e); return myo_fail(MYO_ERR_CUDA, msg); }
+  *out = e;
+  return MYO_OK;
+}
+void myo_env_destroy(myo_env* e) {
+  if (!e) return;
+  for (void* p : e->owned) cudaFree(p);
+  delete e;
+}
+int64_t myo_env_field_count(const myo_env* e, int field) { return e ? envFieldCount(e->P, field) : 0; }
+int myo_env_bind(myo_env* e, int field, void* dev_ptr, int64_t nbytes) {
+  if (!e || field < 0 || field >= MYO_E_COUNT) return myo_fail(MYO_ERR_ARG, "bad env field id");
+  if (dev_ptr) {
+    const int64_t need = envFieldCount(e->P, field) * (int64_t)e->P.nworld * 4;
+    if (need == 0) return myo_fail(MYO_ERR_ARG, "env field is empty for this configuration");
+    if (nbytes != need) return myo_fail(MYO_ERR_ARG, "size mismatch binding an env field");
+    if (((uintptr_t)dev_ptr & 3) != 0) return myo_fail(MYO_ERR_ARG, "buffer must be 4-byte aligned");
+  }
+  e->P.E[field] = dev_ptr;
+  return MYO_OK;
+}
+int myo_env_seed(myo_env* e, uint64_t seed) {
+  if (!e) return myo_fail(MYO_ERR_ARG, "bad argument");
+  e->P.seed = seed;
+  return MYO_OK;
+}
+static int envReady(myo_env* e) {
+  if (!e) return myo_fail(MYO_ERR_ARG, "bad argument");
+  EnvParams& P = e->P;
+  for (int f = 0; f < MYO_E_COUNT; f++)
+    if (envFieldCount(P, f) > 0 && !P.E[f]) return myo_fail(MYO_ERR_UNBOUND, "an env field has no bound device buffer");
+  const FieldPtrs& F = e->b->F;   // the state buffers may have been re-bound since the last call
+  P.qpos = (float*)F.p[MYO_F_QPOS]; P.qvel = (float*)F.p[MYO_F_QVEL]; P.act = (float*)F.p[MYO_F_ACT]; P.ctrl = (float*)F.p[MYO_F_CTRL];
+  P.time = (float*)F.p[MYO_F_TIME]; P.warm = (float*)F.p[MYO_F_QACC_WARMSTART]; P.status = (int*)F.p[MYO_F_STATUS];
+  if (!P.qpos || !P.qvel || !P.time || !P.warm || (P.na && !P.act) || (P.nu && !P.ctrl)) return myo_fail(MYO_ERR_UNBOUND, "a state field has no bound device buffer");
+  if (cudaSetDevice(e->b->model->device) != cudaSuccess) return myo_fail(MYO_ERR_CUDA, "cudaSetDevice failed: libmyostep has no CPU fallback");
+  return MYO_OK;
+}
+int myo_env_reset(myo_env* e, const int32_t* world_mask_dev, void* stream) {
+  int rc = envReady(e);
+  if (rc) return rc;
+  const EnvParams& P = e->P;
+  envResetKernel<<<(P.nworld + 127) / 128, 128, 0, (cudaStream_t)stream>>>(P, world_mask_dev);
+  myo_count_launch(1);
+  return cudaPeekAtLastError() == cudaSuccess ? MYO_OK : myo_fail(MYO_ERR_CUDA, std::string("kernel launch failed: ") + cudaGetErrorString(cudaGetLastError()));
+}
+int myo_env_step(myo_env* e, void* stream) {
+  int rc = envReady(e);
+  if (rc) return rc;
+  const EnvParams& P = e->P;
+  if (P.nu > 0) {
+    const size_t n = (size_t)P.nworld * P.nu;
+    envPreKernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(P);
+    myo_count_launch(1);
+  }
+  rc = myo_step(e->b, P.frame_skip, stream);
+  if (rc) return rc;
+  envPostKernel<<<(P.nworld + 127) / 128, 128, 0, (cudaStream_t)stream>>>(P, 1);
+  myo_count_launch(1);
+  return cudaPeekAtLastError() == cudaSuccess ? MYO_OK : myo_fail(MYO_ERR_CUDA, std::string("kernel launch failed: ") + cudaGetErrorString(cudaGetLastError()));
+}
+int myo_env_forward(myo_env* e, void* stream) {
+  int rc = envReady(e);
+  if (rc) return rc;
+  envPostKernel<<<(e->P.nworld + 127) / 128, 128, 0, (cudaStream_t)stream>>>(e->P, 0);
+  myo_count_launch(1);
+  return cudaPeekAtLastError() == cudaSuccess ? MYO_OK : myo_fail(MYO_ERR_CUDA, std::string("kernel launch failed: ") + cudaGetErrorString(cudaGetLastError()));
+}
+
+}  // extern "C"

@@ -32,6 +32,29 @@ MYO_DECLARE_TEAM(2)
 MYO_DECLARE_TEAM(4)
 MYO_DECLARE_TEAM(8)
 MYO_DECLARE_TEAM(16)
+struct myo_model {
+  DevModel D;
+  SmemLayout L;
+  std::vector<void*> owned;
+  int device;
+};
+struct myo_batch {
+  const myo_model* model;
+  DevModel D;   // copy with this batch's nconmax / njmax
+  SmemLayout L;
+  FieldPtrs F;
+  int nworld;
+  int slot;      // constant-memory parameter slot
+  const TeamVariant* kern;   // step kernel variant (lanes per world) chosen for this batch size
+  bool dirty;    // parameters changed since the last upload
+  bool wide;     // some wide output field is bound: the output kernel runs after the step kernel
+  float* scratch; // per-world intermediates, [nwarps][L.total][worlds per warp]
+  std::vector<void*> owned;
+};
+
+// helpers shared by api.cu and env.cu
+int myo_fail(int code, const std::string& msg);
+void myo_count_launch(int n);
 // out.cu: wide mjData outputs, one thread per (world, item), written after the step kernel from its scratch
 extern const int kWideOutFields[];
 extern const int kNumWideOutFields;

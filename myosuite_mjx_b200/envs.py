@@ -1,0 +1,189 @@
+"""Fused pose-env layer (include/myostep.h "Fused env layer"): ctypes binding of myo_env_* and the batched
+counterpart of the reference's PoseEnvV0 (myosuite/envs/myo/myobase/pose_v0.py) on BaseV0
+(myosuite/envs/myo/base_v0.py).  Everything runs on the device: one env step = pre kernel (action -> ctrl, muscle
+conditions), frame_skip fused mj_steps, post kernel (obs, reward terms, done, masked auto-reset).  No CPU fallback.
+"""
+from __future__ import annotations
+
+import ctypes
+
+import numpy as np
+import torch
+
+from . import lib as _lib
+
+COND = {"": 0, None: 0, "none": 0, "sarcopenia": 1, "fatigue": 2, "reafferentation": 3}
+OBS_KEY = {"time": 0, "qpos": 1, "qvel": 2, "act": 3, "pose_err": 4}
+E_FIELDS = ("action", "obs", "reward", "done", "rwd_terms", "target", "fatigue", "steps", "episode")
+E_INT = ("steps", "episode")
+RWD_TERMS = ("pose", "bonus", "penalty", "act_reg", "sparse", "solved")
+
+_i32p, _f32p = ctypes.POINTER(ctypes.c_int32), ctypes.POINTER(ctypes.c_float)
+
+
+class EnvDesc(ctypes.Structure):
+    """struct myo_env_desc"""
+    _fields_ = [("frame_skip", ctypes.c_int32), ("normalize_act", ctypes.c_int32), ("muscle_condition", ctypes.c_int32),
+                ("epl_id", ctypes.c_int32), ("eip_id", ctypes.c_int32), ("nobs_keys", ctypes.c_int32), ("obs_keys", ctypes.c_int32 * 8),
+                ("ntarget", ctypes.c_int32), ("target_type", ctypes.c_int32), ("reset_type", ctypes.c_int32), ("auto_reset", ctypes.c_int32),
+                ("horizon", ctypes.c_int32), ("world_offset", ctypes.c_int32), ("seed", ctypes.c_uint64),
+                ("pose_thd", ctypes.c_float), ("far_th", ctypes.c_float), ("w_pose", ctypes.c_float), ("w_bonus", ctypes.c_float),
+                ("w_act_reg", ctypes.c_float), ("w_penalty", ctypes.c_float), ("fatigue_F", ctypes.c_float), ("fatigue_R", ctypes.c_float),
+                ("fatigue_r", ctypes.c_float),
+                ("target_qposadr", _i32p), ("target_range", _f32p), ("target_value", _f32p), ("init_qpos", _f32p), ("init_qvel", _f32p),
+                ("reset_lo", _f32p), ("reset_hi", _f32p), ("act_is_muscle", _i32p), ("ctrl_lo", _f32p), ("ctrl_hi", _f32p),
+                ("tau_act", _f32p), ("tau_deact", _f32p)]
+
+
+def _bind_protos(L):
+    if getattr(L, "_env_protos", False):
+        return
+    vp, i32, i64 = ctypes.c_void_p, ctypes.c_int, ctypes.c_int64
+    L.myo_env_create.argtypes = [vp, ctypes.POINTER(EnvDesc), ctypes.POINTER(vp)]
+    L.myo_env_destroy.argtypes = [vp]; L.myo_env_destroy.restype = None
+    L.myo_env_field_count.argtypes = [vp, i32]; L.myo_env_field_count.restype = i64
+    L.myo_env_bind.argtypes = [vp, i32, vp, i64]
+    L.myo_env_seed.argtypes = [vp, ctypes.c_uint64]
+    L.myo_env_reset.argtypes = [vp, vp, vp]
+    L.myo_env_step.argtypes = [vp, vp]
+    L.myo_env_forward.argtypes = [vp, vp]
+    L._env_protos = True
+
+
+def apply_sarcopenia(mj):
+    """base_v0.py:61-66: a weaker muscle has half the peak force (actuator_gainprm[:, 2] *= 0.5); returns a copy of
+    the host model to hand to put_model."""
+    import copy
+    m = copy.copy(mj)
+    g = np.array(mj.actuator_gainprm, dtype=np.float64, copy=True)
+    b = np.array(mj.actuator_biasprm, dtype=np.float64, copy=True)
+    mus = np.asarray(mj.actuator_dyntype) == 4
+    g[mus, 2] *= 0.5
+    m.actuator_gainprm = g
+    m.actuator_biasprm = b
+    return m
+
+
+def pose_config(mj, frame_skip=10, normalize_act=True, muscle_condition="", target_jnt_range=None, target_jnt_value=None,
+                reset_type="init", obs_keys=("qpos", "qvel", "pose_err"), weights=None, pose_thd=0.35, far_th=4 * np.pi / 2,
+                horizon=100, auto_reset=True, seed=0, world_offset=0, epl_id=-1, eip_id=-1, init_qpos=None, init_qvel=None):
+    """Plain-dict env configuration (what myo_env_desc is filled from).
+    Defaults are the reference's: pose_v0.py:15-21 (obs keys, reward weights), :55 (pose_thd), base_v0.py:34-38 ("act" is
+    appended to obs_keys when the model has activations), frame_skip 10 (base_v0.py:28)."""
+    nq, nv, nu, na = int(mj.nq), int(mj.nv), int(mj.nu), int(mj.na)
+    obs_keys = list(obs_keys)
+    if na > 0 and "act" not in obs_keys:
+        obs_keys.append("act")
+    w = dict(pose=1.0, bonus=4.0, act_reg=1.0, penalty=50.0)
+    w.update(weights or {})
+    jr = np.asarray(mj.jnt_range, dtype=np.float32).reshape(-1, 2)
+    qadr = np.asarray(mj.jnt_qposadr, dtype=np.int32)
+    lo, hi = np.array(mj.qpos0, dtype=np.float32), np.array(mj.qpos0, dtype=np.float32)
+    for j in range(int(mj.njnt)):
+        if int(mj.jnt_type[j]) in (2, 3):            # slide / hinge: one qpos each (pose_v0.py:248-251 draws over jnt_range)
+            lo[qadr[j]], hi[qadr[j]] = jr[j, 0], jr[j, 1]
+    if target_jnt_range is not None:
+        tr = np.asarray(target_jnt_range, dtype=np.float32).reshape(-1, 2)
+        target_type, tv = "generate", tr.mean(axis=1)
+    else:
+        tr = None
+        target_type, tv = "fixed", np.asarray(target_jnt_value if target_jnt_value is not None else mj.qpos0, dtype=np.float32)
+    ntarget = len(tv)
+    if ntarget != nq:
+        raise ValueError("pose targets cover every joint in the reference's pose envs (pose_err = target - qpos)")
+    dynprm = np.asarray(mj.actuator_dynprm, dtype=np.float32).reshape(nu, -1) if nu else np.zeros((0, 3), np.float32)
+    cr = np.asarray(mj.actuator_ctrlrange, dtype=np.float32).reshape(nu, 2) if nu else np.zeros((0, 2), np.float32)
+    return dict(frame_skip=int(frame_skip), normalize_act=bool(normalize_act), cond=muscle_condition or "", epl=int(epl_id), eip=int(eip_id),
+                obs_keys=obs_keys, target_qposadr=np.arange(nq, dtype=np.int32), target_type=target_type, target_range=tr, target_value=tv,
+                reset_type=reset_type, auto_reset=bool(auto_reset), horizon=int(horizon), world_offset=int(world_offset), seed=int(seed),
+                pose_thd=float(pose_thd), far_th=float(far_th), weights=(w["pose"], w["bonus"], w["act_reg"], w["penalty"]),
+                init_qpos=np.asarray(init_qpos if init_qpos is not None else mj.qpos0, dtype=np.float32),
+                init_qvel=np.asarray(init_qvel if init_qvel is not None else np.zeros(nv), dtype=np.float32),
+                reset_lo=lo, reset_hi=hi, act_is_muscle=(np.asarray(mj.actuator_dyntype) == 4).astype(np.int32) if nu else np.zeros(0, np.int32),
+                ctrl_lo=cr[:, 0].copy(), ctrl_hi=cr[:, 1].copy(), tau_act=dynprm[:, 0].copy(), tau_deact=dynprm[:, 1].copy(),
+                fatigue_F=0.00912, fatigue_R=0.1 * 0.00094, fatigue_r=10.0 * 15, na=na, dt=float(mj.opt_timestep) * int(frame_skip))
+
+
+class FusedEnv:
+    """myo_env handle bound to a `mjx.Data` batch; env buffers are torch tensors in the [k, nworld] layout."""
+
+    def __init__(self, data, cfg):
+        L = _lib.lib()
+        _bind_protos(L)
+        self.data, self.cfg = data, cfg
+        d = EnvDesc()
+        keep = []
+
+        def arr(v, dt):
+            if v is None:
+                return None
+            a = np.ascontiguousarray(np.asarray(v, dtype=dt))
+            keep.append(a)
+            return a.ctypes.data_as(_i32p if dt == np.int32 else _f32p)
+        d.frame_skip, d.normalize_act, d.muscle_condition = cfg["frame_skip"], int(cfg["normalize_act"]), COND[cfg["cond"]]
+        d.epl_id, d.eip_id = cfg["epl"], cfg["eip"]
+        d.nobs_keys = len(cfg["obs_keys"])
+        for i, k in enumerate(cfg["obs_keys"]):
+            d.obs_keys[i] = OBS_KEY[k]
+        d.ntarget = len(cfg["target_qposadr"])
+        d.target_type = 1 if cfg["target_type"] == "generate" else 0
+        d.reset_type = 1 if cfg["reset_type"] == "random" else 0
+        d.auto_reset, d.horizon, d.world_offset, d.seed = int(cfg["auto_reset"]), cfg["horizon"], cfg["world_offset"], cfg["seed"]
+        d.pose_thd, d.far_th = cfg["pose_thd"], cfg["far_th"]
+        d.w_pose, d.w_bonus, d.w_act_reg, d.w_penalty = cfg["weights"]
+        d.fatigue_F, d.fatigue_R, d.fatigue_r = cfg["fatigue_F"], cfg["fatigue_R"], cfg["fatigue_r"]
+        d.target_qposadr = arr(cfg["target_qposadr"], np.int32)
+        d.target_range, d.target_value = arr(cfg["target_range"], np.float32), arr(cfg["target_value"], np.float32)
+        d.init_qpos, d.init_qvel = arr(cfg["init_qpos"], np.float32), arr(cfg["init_qvel"], np.float32)
+        d.reset_lo, d.reset_hi = arr(cfg["reset_lo"], np.float32), arr(cfg["reset_hi"], np.float32)
+        d.act_is_muscle = arr(cfg["act_is_muscle"], np.int32)
+        d.ctrl_lo, d.ctrl_hi = arr(cfg["ctrl_lo"], np.float32), arr(cfg["ctrl_hi"], np.float32)
+        d.tau_act, d.tau_deact = arr(cfg["tau_act"], np.float32), arr(cfg["tau_deact"], np.float32)
+        h = ctypes.c_void_p()
+        _lib.check(L.myo_env_create(data._h, ctypes.byref(d), ctypes.byref(h)))
+        self._h = h
+        dev = data.qpos.device
+        self._t = {}
+        for fid, name in enumerate(E_FIELDS):
+            cnt = L.myo_env_field_count(h, fid)
+            if cnt == 0:
+                continue
+            t = torch.zeros((cnt, data.nworld), dtype=torch.int32 if name in E_INT else torch.float32, device=dev)
+            _lib.check(L.myo_env_bind(h, fid, ctypes.c_void_p(t.data_ptr()), t.numel() * 4))
+            self._t[name] = t
+
+    def storage(self, name):
+        return self._t[name]
+
+    def __getattr__(self, name):
+        t = self.__dict__.get("_t", {})
+        if name in t:
+            return t[name].t()      # logical [nworld, k] view
+        raise AttributeError(name)
+
+    def _stream(self):
+        return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+    def seed(self, seed):
+        _lib.check(_lib.lib().myo_env_seed(self._h, ctypes.c_uint64(int(seed) & ((1 << 64) - 1))))
+
+    def reset(self, mask=None):
+        if mask is not None:
+            mask = mask.to(device=self.data.qpos.device, dtype=torch.int32).reshape(-1).contiguous()
+        _lib.check(_lib.lib().myo_env_reset(self._h, ctypes.c_void_p(mask.data_ptr()) if mask is not None else None, self._stream()))
+
+    def step(self, action=None):
+        if action is not None:
+            a = torch.as_tensor(action, dtype=torch.float32, device=self.data.qpos.device)
+            self._t["action"].copy_(a.reshape(self.data.nworld, -1).t())
+        _lib.check(_lib.lib().myo_env_step(self._h, self._stream()))
+
+    def forward(self):
+        """obs / reward terms / done of the current state (MujocoEnv.forward); no physics, no reset"""
+        _lib.check(_lib.lib().myo_env_forward(self._h, self._stream()))
+
+    def __del__(self):
+        try:
+            _lib.lib().myo_env_destroy(self._h)
+        except Exception:
+            pass

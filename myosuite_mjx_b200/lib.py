@@ -69,4 +69,6 @@ def check(rc):
 
 EXPORTS = ["myo_model_create", "myo_model_destroy", "myo_batch_create", "myo_batch_destroy", "myo_batch_nconmax",
            "myo_batch_njmax", "myo_batch_smem_bytes", "myo_batch_team", "myo_field_count", "myo_field_itemsize", "myo_field_is_int", "myo_field_name", "myo_batch_bind",
-           "myo_forward", "myo_step", "myo_reset", "myo_step_host", "myo_launch_count", "myo_last_error", "myo_kat_quat"]
+           "myo_forward", "myo_step", "myo_reset", "myo_step_host", "myo_launch_count", "myo_last_error", "myo_kat_quat",
+           "myo_env_create", "myo_env_destroy", "myo_env_field_count", "myo_env_bind", "myo_env_seed", "myo_env_reset", "myo_env_step",
+           "myo_env_forward"]

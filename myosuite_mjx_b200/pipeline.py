@@ -80,65 +80,48 @@ class PipelineEnv:
 
 
 class PoseEnv(PipelineEnv):
-    """Joint-pose task with the reset(rng)/step(state, action) shape of the reference's MJX TrackEnv, on the pose
-    configs (reference: myosuite/envs/myo/myobase/pose_v0.py:98-138 reward terms, :248-251 random reset,
-    myosuite/envs/myo/base_v0.py:85-91 muscle squash).  Observation = concat(qpos, qvel) as myodm_v0.py:297-304."""
+    """Joint-pose task (reference: myosuite/envs/myo/myobase/pose_v0.py on myosuite/envs/myo/base_v0.py) with the
+    reset(rng) -> State / step(State, action) -> State shape of the reference's MJX TrackEnv (myodm_v0.py:152-173,
+    269-295).  One env step is three launches on the device (envs.FusedEnv: action -> ctrl with the muscle squash and the
+    muscle conditions, frame_skip fused mj_steps, obs / reward terms / done / masked auto-reset); nothing runs on the
+    host.  Observation = concat of obs_keys (default qpos, qvel * dt, pose_err, act; pose_v0.py:15, base_v0.py:34-38)."""
 
-    def __init__(self, sys, n_frames=10, nworld=1, reset_type="random", normalize_act=True, pose_thd=0.35, far_th=2 * np.pi, **kw):
+    def __init__(self, sys, n_frames=10, nworld=1, reset_type="random", target_type="generate", normalize_act=True, pose_thd=0.35,
+                 muscle_condition="", target_jnt_range=None, target_jnt_value=None, horizon=100, auto_reset=True, world_offset=0,
+                 obs_keys=("qpos", "qvel", "pose_err"), weights=None, epl_id=-1, eip_id=-1, **kw):
+        from . import envs
+        if muscle_condition == "sarcopenia" and not isinstance(sys, mjx.Model):
+            sys = envs.apply_sarcopenia(sys)
         super().__init__(sys, n_frames=n_frames, nworld=nworld, **kw)
         mj = self.sys.mj
-        self.reset_type, self.normalize_act, self.pose_thd, self.far_th = reset_type, normalize_act, pose_thd, far_th
-        cr = torch.as_tensor(np.asarray(mj.actuator_ctrlrange, dtype=np.float32), device=self.device)
-        self._ctrl_lo, self._ctrl_hi = cr[:, 0], cr[:, 1]
-        self._is_muscle = torch.as_tensor(np.asarray(mj.actuator_dyntype) == 4, device=self.device)
-        hinge = [j for j in range(mj.njnt) if mj.jnt_type[j] in (2, 3)]
-        self._qadr = torch.as_tensor([int(mj.jnt_qposadr[j]) for j in hinge], device=self.device)
-        rng_ = np.asarray(mj.jnt_range, dtype=np.float32)[hinge]
-        lim = np.asarray(mj.jnt_limited)[hinge].astype(bool)
-        lo = np.where(lim, rng_[:, 0], -0.5); hi = np.where(lim, rng_[:, 1], 0.5)
-        self._jlo = torch.as_tensor(lo, dtype=torch.float32, device=self.device)
-        self._jhi = torch.as_tensor(hi, dtype=torch.float32, device=self.device)
-        self._qpos0 = torch.as_tensor(np.asarray(mj.qpos0, dtype=np.float32), device=self.device)
-        self.target = self._qpos0[self._qadr].expand(self.nworld, -1).clone()
+        if target_type == "generate" and target_jnt_range is None:
+            c0 = envs.pose_config(mj)
+            target_jnt_range = np.stack([c0["reset_lo"], c0["reset_hi"]], axis=1)   # every joint over its full range
+        if target_type == "fixed":
+            target_jnt_range = None
+        self.cfg = envs.pose_config(mj, frame_skip=n_frames, normalize_act=normalize_act, muscle_condition=muscle_condition,
+                                    target_jnt_range=target_jnt_range, target_jnt_value=target_jnt_value, reset_type=reset_type,
+                                    obs_keys=obs_keys, weights=weights, pose_thd=pose_thd, horizon=horizon, auto_reset=auto_reset,
+                                    world_offset=world_offset, epl_id=epl_id, eip_id=eip_id)
+        self.env = envs.FusedEnv(self._data, self.cfg)
 
-    def _generator(self, rng):
-        if isinstance(rng, torch.Generator):
-            return rng
-        g = torch.Generator(device=self.device)
-        g.manual_seed(int(rng))
-        return g
+    @property
+    def target(self):
+        return self.env.target
 
-    def _get_obs(self, d):
-        return torch.cat((d.qpos, d.qvel), dim=1)
-
-    def _uniform_pose(self, g):
-        u = torch.rand((self.nworld, self._qadr.numel()), generator=g, device=self.device)
-        return self._jlo + u * (self._jhi - self._jlo)
+    def _metrics(self):
+        terms = self.env.rwd_terms
+        from .envs import RWD_TERMS
+        return {k: terms[:, i] for i, k in enumerate(RWD_TERMS)}
 
     def reset(self, rng) -> State:
-        g = self._generator(rng)
-        q = self._qpos0.expand(self.nworld, -1).clone()
-        if self.reset_type == "random":
-            q[:, self._qadr] = self._uniform_pose(g)
-        self.target = self._uniform_pose(g)
-        d = self.pipeline_init(q, torch.zeros((self.nworld, self.sys.nv), device=self.device))
-        zero = torch.zeros(self.nworld, device=self.device)
-        metrics = {"pose": zero.clone(), "bonus": zero.clone(), "act_reg": zero.clone(), "penalty": zero.clone()}
-        return State(d, self._get_obs(d), zero.clone(), zero.clone(), metrics)
+        self.env.seed(int(rng))
+        self.env.storage("episode").zero_()
+        self.env.reset()
+        d = mjx.forward(self.sys, self._data)
+        return State(d, self.env.obs, self.env.reward[:, 0], self.env.done[:, 0], self._metrics())
 
     def step(self, state: State, action) -> State:
-        a = torch.as_tensor(action, dtype=torch.float32, device=self.device).reshape(self.nworld, self.sys.nu)
-        if self.normalize_act:
-            squashed = 1.0 / (1.0 + torch.exp(-5.0 * (a - 0.5)))                      # base_v0.py:85-91
-            affine = (a.clamp(-1, 1) + 1) * (self._ctrl_hi - self._ctrl_lo) * 0.5 + self._ctrl_lo   # myodm_v0.py:273-275
-            a = torch.where(self._is_muscle, squashed, affine)
-        d = self.pipeline_step(state.pipeline_state, a)
-        err = d.qpos[:, self._qadr] - self.target
-        dist = torch.linalg.norm(err, dim=1)
-        act_mag = torch.linalg.norm(d.act, dim=1) / max(1, self.sys.na) if self.sys.na else torch.zeros_like(dist)
-        far = (dist > self.far_th).float()
-        metrics = {"pose": -dist, "bonus": (dist < self.pose_thd).float() + (dist < 1.5 * self.pose_thd).float(),
-                   "act_reg": -act_mag, "penalty": -far}
-        reward = 1.0 * metrics["pose"] + 4.0 * metrics["bonus"] + 1.0 * metrics["act_reg"] + 50.0 * metrics["penalty"]
-        state.metrics.update(**metrics)
-        return state.replace(pipeline_state=d, obs=self._get_obs(d), reward=reward, done=far)
+        self.env.step(action)
+        state.metrics.update(**self._metrics())
+        return state.replace(pipeline_state=self._data, obs=self.env.obs, reward=self.env.reward[:, 0], done=self.env.done[:, 0])

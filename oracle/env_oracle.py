@@ -1,0 +1,159 @@
+"""CPU restatement (numpy, float64) of the reference's pose-env layer.  TEST INFRASTRUCTURE ONLY: imported by tests/,
+__graft_entry__.smoke() and bench.py's cpu legs, never by the product.
+
+Follows (reference file:line):
+    action -> ctrl            myosuite/envs/myo/base_v0.py:81-110; myosuite/robot/robot.py:771-783 (default_robot)
+    fatigue 3CC-r             myosuite/envs/myo/fatigue.py:61-108
+    obs_dict / reward_dict    myosuite/envs/myo/myobase/pose_v0.py:98-138
+    reset / target sampling   myosuite/envs/myo/myobase/pose_v0.py:141-168,190-251
+Pinned: tests/test_env_oracle.py checks every function here against tests/golden/env_kat.npz, which was produced by
+running the reference's own BaseV0.step / CumulativeFatigue / PoseEnvV0 code (tests/golden/make_env_kat.py).
+The uniform draws are the library's counter-based hash (csrc/env.cu envUniform), not numpy's generator: the reference
+draws from np_random, whose stream a batched device RNG cannot reproduce; the distribution (uniform on the range) is
+the same.
+"""
+import numpy as np
+
+M64 = (1 << 64) - 1
+
+
+def uniform(seed, gworld, episode, stream, idx):
+    """envUniform of csrc/env.cu: splitmix64 finaliser of (seed, world, episode, stream, index) -> float32 in [0, 1)."""
+    z = (int(seed) ^ (int(gworld) * 0xD1B54A32D192ED03) ^ (int(episode) * 0x8CB92BA72F3D8DD7) ^ (((int(stream) << 32) | int(idx)) * 0x9E3779B97F4A7C15)) & M64
+    z = (z + 0x9E3779B97F4A7C15) & M64
+    z = ((z ^ (z >> 30)) * 0xBF58476D1CE4E5B9) & M64
+    z = ((z ^ (z >> 27)) * 0x94D049BB133111EB) & M64
+    z ^= z >> 31
+    return np.float32(z >> 40) * np.float32(1.0 / 16777216.0)
+
+
+def action_to_ctrl(a, is_muscle, na, normalize_act, ctrl_lo, ctrl_hi, cond="", epl=-1, eip=-1, fatigue=None):
+    """base_v0.py:81-110 + robot.py:771-783.  `a`: [..., nu]; returns ctrl_desired after the robot's re-projection."""
+    x = np.array(a, dtype=np.float64)
+    mus = np.asarray(is_muscle, dtype=bool)
+    if na and normalize_act:
+        x[..., mus] = 1.0 / (1.0 + np.exp(-5.0 * (x[..., mus] - 0.5)))
+        robot_normalized = False
+    else:
+        robot_normalized = bool(normalize_act)
+    if cond == "fatigue":
+        x[..., mus] = fatigue.compute_act(x[..., mus])[0]
+    elif cond == "reafferentation":
+        x[..., epl] = x[..., eip].copy()
+        x[..., eip] = 0
+    if robot_normalized:
+        x = 0.5 * (np.asarray(ctrl_lo) + np.asarray(ctrl_hi)) + x * (np.asarray(ctrl_hi) - np.asarray(ctrl_lo)) / 2.0
+    return x
+
+
+class Fatigue:
+    """fatigue.py:9-108 (3CC-r); state arrays of shape [..., nmuscle]."""
+
+    def __init__(self, tau_act, tau_deact, dt, shape=(), F=0.00912, R=0.1 * 0.00094, r=10 * 15):
+        self.tauact, self.taudeact, self.dt, self.F, self.R, self.r = np.asarray(tau_act, float), np.asarray(tau_deact, float), dt, F, R, r
+        n = len(self.tauact)
+        self.MA, self.MR, self.MF = np.zeros(shape + (n,)), np.ones(shape + (n,)), np.zeros(shape + (n,))
+
+    def reset(self, mask=None):
+        m = slice(None) if mask is None else np.asarray(mask, bool)
+        self.MA[m], self.MR[m], self.MF[m] = 0.0, 1.0, 0.0
+
+    def compute_act(self, act):
+        TL = np.asarray(act, float)
+        MA, MR, MF, dt, F = self.MA, self.MR, self.MF, self.dt, self.F
+        LD = 1 / self.tauact * (0.5 + 1.5 * MA)
+        LR = (0.5 + 1.5 * MA) / self.taudeact
+        C = np.where(MA < TL, np.where(MR > TL - MA, LD * (TL - MA), LD * MR), LR * (TL - MA))
+        rR = np.where(MA >= TL, self.r * self.R, self.R)
+        C = np.clip(C, np.maximum(-MA / dt + F * MA, (MR - 1) / dt + rR * MF), np.minimum((1 - MA) / dt + F * MA, MR / dt + rR * MF))
+        dMA, dMR, dMF = (C - F * MA) * dt, (-C + rR * MF) * dt, (F * MA - rR * MF) * dt
+        self.MA, self.MR, self.MF = MA + dMA, MR + dMR, MF + dMF
+        return self.MA, self.MR, self.MF
+
+
+def obs_dict(time, qpos, qvel, act, target, dt, target_qposadr=None):
+    """pose_v0.py:106-116."""
+    qpos = np.asarray(qpos, float)
+    sel = qpos if target_qposadr is None else qpos[..., np.asarray(target_qposadr)]
+    na = 0 if act is None else np.shape(act)[-1]
+    return {"time": np.asarray(time, float)[..., None], "qpos": qpos, "qvel": np.asarray(qvel, float) * dt,
+            "act": np.asarray(act, float) if na > 0 else np.zeros_like(qpos), "pose_err": np.asarray(target, float) - sel}
+
+
+def reward_dict(od, na, pose_thd=0.35, weights=(1.0, 4.0, 1.0, 50.0)):
+    """pose_v0.py:118-138; weights in DEFAULT_RWD_KEYS_AND_WEIGHTS order: pose, bonus, act_reg, penalty."""
+    pose_dist = np.linalg.norm(od["pose_err"], axis=-1)
+    act_mag = np.linalg.norm(od["act"], axis=-1)
+    if na != 0:
+        act_mag = act_mag / na
+    far_th = 4 * np.pi / 2
+    r = {"pose": -1.0 * pose_dist, "bonus": 1.0 * (pose_dist < pose_thd) + 1.0 * (pose_dist < 1.5 * pose_thd),
+         "penalty": -1.0 * (pose_dist > far_th), "act_reg": -1.0 * act_mag, "sparse": -1.0 * pose_dist,
+         "solved": pose_dist < pose_thd, "done": pose_dist > far_th}
+    r["dense"] = weights[0] * r["pose"] + weights[1] * r["bonus"] + weights[2] * r["act_reg"] + weights[3] * r["penalty"]
+    return r
+
+
+class PoseEnvOracle:
+    """Batched pose env on top of a physics stepper `physics_step(qpos, qvel, act, ctrl, time, n) -> (qpos, qvel, act, time)`
+    (the mj_step oracle in tests); mirrors the library's myo_env_reset / myo_env_step including masked auto-reset."""
+
+    def __init__(self, cfg, nworld, physics_step):
+        self.c, self.nw, self.physics = cfg, nworld, physics_step
+        c = cfg
+        self.nq, self.nv, self.na, self.nu = len(c["init_qpos"]), len(c["init_qvel"]), c["na"], len(c["act_is_muscle"])
+        self.qpos = np.zeros((nworld, self.nq)); self.qvel = np.zeros((nworld, self.nv)); self.act = np.zeros((nworld, self.na))
+        self.ctrl = np.zeros((nworld, self.nu)); self.time = np.zeros(nworld)
+        self.target = np.zeros((nworld, len(c["target_qposadr"])))
+        self.steps = np.zeros(nworld, int); self.episode = np.zeros(nworld, int)
+        self.fat = None
+        if c.get("cond") == "fatigue":
+            mus = np.asarray(c["act_is_muscle"], bool)
+            self.fat = Fatigue(np.asarray(c["tau_act"])[mus], np.asarray(c["tau_deact"])[mus], c["dt"], (nworld,), c.get("fatigue_F", 0.00912),
+                               c.get("fatigue_R", 0.1 * 0.00094), c.get("fatigue_r", 150))
+
+    def _reset_world(self, w):
+        c = self.c
+        gw, ep = c.get("world_offset", 0) + w, self.episode[w]
+        for k in range(self.target.shape[1]):
+            if c["target_type"] == "generate":
+                lo, hi = np.float32(c["target_range"][k][0]), np.float32(c["target_range"][k][1])
+                self.target[w, k] = lo + (hi - lo) * uniform(c["seed"], gw, ep, 0, k)
+            else:
+                self.target[w, k] = c["target_value"][k]
+        for j in range(self.nq):
+            if c["reset_type"] == "random":
+                lo, hi = np.float32(c["reset_lo"][j]), np.float32(c["reset_hi"][j])
+                self.qpos[w, j] = lo + (hi - lo) * uniform(c["seed"], gw, ep, 1, j)
+            else:
+                self.qpos[w, j] = c["init_qpos"][j]
+        self.qvel[w] = c["init_qvel"]; self.act[w] = 0; self.ctrl[w] = 0; self.time[w] = 0
+        if self.fat is not None:
+            m = np.zeros(self.nw, bool); m[w] = True
+            self.fat.reset(m)
+        self.steps[w] = 0; self.episode[w] += 1
+
+    def _obs(self):
+        c = self.c
+        od = obs_dict(self.time, self.qpos, self.qvel, self.act if self.na else None, self.target, c["dt"], c["target_qposadr"])
+        return od, np.concatenate([od[k] for k in c["obs_keys"]], axis=-1)
+
+    def reset(self, mask=None):
+        for w in range(self.nw):
+            if mask is None or mask[w]:
+                self._reset_world(w)
+        return self._obs()[1]
+
+    def step(self, action):
+        c = self.c
+        self.ctrl = action_to_ctrl(action, c["act_is_muscle"], self.na, c["normalize_act"], c["ctrl_lo"], c["ctrl_hi"], c.get("cond", ""),
+                                   c.get("epl", -1), c.get("eip", -1), self.fat)
+        self.qpos, self.qvel, self.act, self.time = self.physics(self.qpos, self.qvel, self.act, self.ctrl, self.time, c["frame_skip"])
+        od, _ = self._obs()
+        r = reward_dict(od, self.na, c["pose_thd"], c["weights"])
+        self.steps += 1
+        ended = r["done"] | ((c["horizon"] > 0) & (self.steps >= c["horizon"]))
+        if c["auto_reset"]:
+            for w in np.nonzero(ended)[0]:
+                self._reset_world(w)
+        return self._obs()[1], r, ended

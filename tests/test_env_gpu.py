@@ -1,5 +1,7 @@
 """The MJX-style env surface (reset(rng) -> State, step(State, action) -> State, pipeline_init / pipeline_step) on the
 GPU, and size-independent properties at BASELINE.json's full batch size (8192 worlds)."""
+import os
+
 import numpy as np
 import pytest
 
@@ -36,11 +38,13 @@ def test_pose_env_reset_step_shapes(models):
     m = models("hand_pose")
     env = pipeline.PoseEnv(m, n_frames=10, nworld=64)
     st = env.reset(1234)
-    assert st.obs.shape == (64, m.nq + m.nv) and st.reward.shape == (64,) and st.done.shape == (64,)
-    assert set(st.metrics) == {"pose", "bonus", "act_reg", "penalty"}
+    # obs = qpos, qvel * dt, pose_err, act (pose_v0.py:15 + base_v0.py:34-38)
+    assert st.obs.shape == (64, 2 * m.nq + m.nv + m.na) and st.reward.shape == (64,) and st.done.shape == (64,)
+    assert set(st.metrics) == {"pose", "bonus", "penalty", "act_reg", "sparse", "solved"}
     lo = torch.as_tensor(np.asarray(m.jnt_range)[:, 0], device="cuda", dtype=torch.float32)
     hi = torch.as_tensor(np.asarray(m.jnt_range)[:, 1], device="cuda", dtype=torch.float32)
     assert bool(((st.pipeline_state.qpos >= lo - 1e-6) & (st.pipeline_state.qpos <= hi + 1e-6)).all())
+    assert bool(((env.target >= lo - 1e-6) & (env.target <= hi + 1e-6)).all())
     st2 = env.reset(1234)
     q_first = st2.pipeline_state.qpos.clone()
     g = torch.Generator(device="cuda"); g.manual_seed(7)
@@ -52,12 +56,150 @@ def test_pose_env_reset_step_shapes(models):
     assert float(st2.pipeline_state.time.min()) == pytest.approx(5 * 10 * 0.002, abs=1e-5)
     assert float((st2.pipeline_state.qpos - q_first).abs().max()) > 1e-3
     assert float(st2.pipeline_state.act.min()) >= 0 and float(st2.pipeline_state.act.max()) <= 1
+    obs2 = st2.obs.clone()
     # same seed, same actions -> same trajectory (determinism, the property tests/test_envs.py:110-120 checks)
     st3 = env.reset(1234)
     g.manual_seed(7)
     for _ in range(5):
         st3 = env.step(st3, torch.rand((64, m.nu), generator=g, device="cuda") * 2 - 1)
-    assert torch.equal(st3.obs, st2.obs)
+    assert torch.equal(st3.obs, obs2)
+
+
+GOLD = np.load(os.path.join(os.path.dirname(__file__), "golden", "env_kat.npz"))
+
+
+@pytest.mark.parametrize("cond", ["", "fatigue", "reafferentation"])
+def test_env_pre_kernel_matches_reference_golden(models, cond):
+    """action -> ctrl on the device against vectors produced by the reference's own BaseV0.step / CumulativeFatigue
+    (tests/golden/make_env_kat.py).  float32 tolerance: 2e-6 absolute on ctrl in [0, 1]; fatigue compartments, which
+    integrate 300 steps in float32 against the reference's float64, 2e-5."""
+    import torch
+    from myosuite_mjx_b200 import envs, mjx
+    m = models("hand_pose")
+    nu, nw = m.nu, 32
+    assert nu == 39 and (np.asarray(m.actuator_dyntype) == 4).all()
+    model = mjx.put_model(m)
+    d = mjx.make_data(model, nw, fields="core")
+    cfg = envs.pose_config(m, frame_skip=int(GOLD["frame_skip"]), muscle_condition=cond, epl_id=7, eip_id=11, auto_reset=False, horizon=0)
+    cfg["tau_act"], cfg["tau_deact"] = GOLD["dynprm"][:nu, 0].astype(np.float32), GOLD["dynprm"][:nu, 1].astype(np.float32)
+    env = envs.FusedEnv(d, cfg)
+    env.reset()
+    T = 300 if cond == "fatigue" else 40
+    for t in range(T):
+        a = torch.as_tensor(GOLD["actions"][t, :nu], dtype=torch.float32, device="cuda").expand(nw, nu)
+        env.step(a)
+        ctrl = d.ctrl.cpu().numpy()
+        assert np.abs(ctrl - GOLD["ctrl_" + (cond or "none")][t, :nu]).max() < (2e-5 if cond == "fatigue" else 2e-6), (cond, t)
+        if cond == "fatigue" and t % 50 == 49:
+            f = env.storage("fatigue").cpu().numpy().reshape(3, nu, nw)
+            assert np.abs(f - GOLD["fatigue_states"][t][:, :, None]).max() < 2e-5
+    assert int(env.steps.min()) == T and int(env.episode.max()) == 1
+
+
+def test_env_forward_matches_reference_golden(models):
+    """obs / reward terms / done of given states against the reference's own PoseEnvV0.get_obs_dict / get_reward_dict.
+    float32: obs exact to rounding of the inputs (1e-6 rel), reward terms rel 2e-6; the thresholded terms (bonus, solved,
+    done, penalty) must agree exactly except where the float64 distance is within 1e-6 of a threshold."""
+    import torch
+    from myosuite_mjx_b200 import envs, mjx
+    m = models("hand_pose")
+    n = GOLD["pose_qpos"].shape[0]
+    model = mjx.put_model(m)
+    d = mjx.make_data(model, n, fields="core")
+    cfg = envs.pose_config(m, obs_keys=("time", "qpos", "qvel", "act", "pose_err"), auto_reset=False, horizon=0)
+    env = envs.FusedEnv(d, cfg)
+    env.reset()
+    dev = d.qpos.device
+    d.qpos.copy_(torch.as_tensor(GOLD["pose_qpos"], dtype=torch.float32, device=dev)); d.qvel.copy_(torch.as_tensor(GOLD["pose_qvel"], dtype=torch.float32, device=dev))
+    d.act.copy_(torch.as_tensor(GOLD["pose_act"], dtype=torch.float32, device=dev)); d.time.copy_(torch.as_tensor(GOLD["pose_time"][:, None], dtype=torch.float32, device=dev))
+    env.target.copy_(torch.as_tensor(GOLD["pose_target"], dtype=torch.float32, device=dev))
+    env.forward()
+    obs = env.obs.cpu().numpy()
+    ref = np.concatenate([GOLD["obs_" + k] for k in ("time", "qpos", "qvel", "act", "pose_err")], axis=1)
+    assert obs.shape == ref.shape
+    assert np.abs(obs - ref).max() < 2e-6 * max(1.0, np.abs(ref).max())
+    terms = env.rwd_terms.cpu().numpy()
+    dist = -GOLD["rwd_pose"]
+    thd, far = float(GOLD["pose_thd"]), 2 * np.pi
+    safe = (np.abs(dist - thd) > 1e-5) & (np.abs(dist - 1.5 * thd) > 1e-5) & (np.abs(dist - far) > 1e-5)
+    assert safe.sum() > 0.95 * n
+    for i, k in enumerate(envs.RWD_TERMS):
+        g = GOLD["rwd_" + k].astype(np.float64)
+        sel = safe if k in ("bonus", "penalty", "solved") else slice(None)
+        assert np.abs(terms[:, i][sel] - g[sel]).max() <= 2e-6 * max(1.0, np.abs(g).max()), k
+    assert np.abs(env.reward.cpu().numpy()[:, 0][safe] - GOLD["rwd_dense"][safe]).max() < 1e-4      # weights up to 50
+    assert np.array_equal(env.done.cpu().numpy()[:, 0][safe] > 0, GOLD["rwd_done"][safe] > 0)
+    assert int(env.steps.max()) == 0                                                              # forward does not count as a step
+
+
+def test_env_rollout_matches_oracle(models):
+    """Full env loop (reset -> step x N with auto-reset on a short horizon) against oracle/env_oracle.PoseEnvOracle driving
+    the mj_step oracle: same targets and reset poses bit for bit (shared counter-based hash), obs within the physics
+    tolerance of tests/test_parity_gpu.py accumulated over frame_skip steps."""
+    import env_oracle as eo
+    import oracle
+    import torch
+    from myosuite_mjx_b200 import envs, mjx
+    m = models("finger")
+    nw, horizon, fs = 6, 4, 5
+    model = mjx.put_model(m)
+    d = mjx.make_data(model, nw, fields="core")
+    base = envs.pose_config(m)
+    tr = np.stack([base["reset_lo"], base["reset_hi"]], axis=1) * 0.6
+    cfg = envs.pose_config(m, frame_skip=fs, target_jnt_range=tr, reset_type="random", horizon=horizon, auto_reset=True, seed=77, world_offset=10)
+    cfg["reset_lo"], cfg["reset_hi"] = 0.5 * cfg["reset_lo"], 0.5 * cfg["reset_hi"]
+    env = envs.FusedEnv(d, cfg)
+    orcs = [oracle.Oracle(m) for _ in range(nw)]
+
+    def physics(qpos, qvel, act, ctrl, time, n):
+        q2, v2, a2, t2 = qpos.copy(), qvel.copy(), act.copy(), time.copy()
+        for w, o in enumerate(orcs):
+            if time[w] == 0:
+                o.reset()
+            o.set_state(qpos[w], qvel[w], act[w], ctrl[w]); o.field("time")[:] = time[w]
+            o.step(n)
+            q2[w], v2[w], a2[w], t2[w] = o.qpos, o.qvel, o.act, o.field("time")[0]
+        return q2, v2, a2, t2
+    ref = eo.PoseEnvOracle(cfg, nw, physics)
+    env.reset(); obs_ref = ref.reset()
+    torch.cuda.synchronize()
+    assert np.array_equal(env.target.cpu().numpy(), ref.target.astype(np.float32))
+    assert np.array_equal(d.qpos.cpu().numpy(), ref.qpos.astype(np.float32))
+    assert np.abs(env.obs.cpu().numpy() - obs_ref).max() < 1e-6
+    rng = np.random.default_rng(5)
+    nreset = 0
+    for t in range(2 * horizon + 1):
+        a = rng.uniform(-1, 1, size=(nw, m.nu))
+        env.step(torch.as_tensor(a, dtype=torch.float32, device="cuda"))
+        obs_ref, r, ended = ref.step(a)
+        got = env.obs.cpu().numpy()
+        assert np.array_equal(env.done.cpu().numpy()[:, 0] > 0, ended), t
+        assert np.array_equal(env.target.cpu().numpy(), ref.target.astype(np.float32))
+        assert np.array_equal(env.episode.cpu().numpy()[:, 0], ref.episode) and np.array_equal(env.steps.cpu().numpy()[:, 0], ref.steps)
+        assert np.abs(got - obs_ref).max() < 5e-3, (t, np.abs(got - obs_ref).max())
+        assert np.abs(env.reward.cpu().numpy()[:, 0] - r["dense"]).max() < 2e-2
+        nreset += int(ended.sum())
+        # the oracle restarts each env step from the library's state so that float32 drift does not accumulate across steps
+        ref.qpos, ref.qvel, ref.act = d.qpos.cpu().numpy().astype(np.float64), d.qvel.cpu().numpy().astype(np.float64), d.act.cpu().numpy().astype(np.float64)
+    assert nreset == 2 * nw
+
+
+def test_env_world_offset_partition(models):
+    """A world's episode stream depends on its global index only: ranks that own [0, 4) and [4, 8) reproduce a single
+    8-world batch (the multi-GPU partition of DESIGN.md section 4 applied to the env layer)."""
+    import torch
+    from myosuite_mjx_b200 import pipeline
+    m = models("finger")
+    full = pipeline.PoseEnv(m, n_frames=5, nworld=8, horizon=3)
+    lo, hi = pipeline.PoseEnv(m, n_frames=5, nworld=4, horizon=3), pipeline.PoseEnv(m, n_frames=5, nworld=4, horizon=3, world_offset=4)
+    sf, sl, sh = full.reset(3), lo.reset(3), hi.reset(3)
+    g = torch.Generator(device="cuda"); g.manual_seed(1)
+    for _ in range(7):
+        a = torch.rand((8, m.nu), generator=g, device="cuda") * 2 - 1
+        sf, sl, sh = full.step(sf, a), lo.step(sl, a[:4]), hi.step(sh, a[4:])
+        assert torch.equal(sf.obs[:4], sl.obs) and torch.equal(sf.obs[4:], sh.obs)
+        assert torch.equal(sf.reward[4:], sh.reward) and torch.equal(sf.done[:4], sl.done)
+    assert int(full.env.episode.min()) == 3
 
 
 def test_full_size_properties(models):
