@@ -24,12 +24,25 @@ namespace {
 enum { ROW_EQ = 0, ROW_LIMJ = 1, ROW_LIMT = 2, ROW_CON = 3 };
 enum { E_D = 0, E_AREF, E_JAR, E_JV, E_FORCE, E_DESC0, E_COEF, E_DESC1, E_POS, E_MARGIN };   // as in team.cu
 
-struct Ctx { const float* sm; size_t stride, w, nw; };
-__device__ __forceinline__ float S(const Ctx& c, int k) { return c.sm[(size_t)k * c.stride]; }
-#define OF(ptr, k) ((float*)(ptr))[(size_t)(k) * c.nw + c.w]
+// STRIDE = worlds that share a warp of the step kernel (32 / team width): a compile-time constant here, so a scratch
+// element's address is the world's base pointer plus an immediate offset
+template <int STRIDE> struct CtxT { const float* sm; size_t w, nw; };
+template <int STRIDE> __device__ __forceinline__ float S(const CtxT<STRIDE>& c, int k) { return c.sm[k * STRIDE]; }
+// `n` consecutive elements of a [k][nworld] field, first one at element index k0: pointer stepping, no multiplies
+struct Row {
+  float* p; size_t nw;
+  __device__ __forceinline__ Row(void* base, size_t k0, size_t nw_, size_t w) : p((float*)base + k0 * nw_ + w), nw(nw_) {}
+#ifndef OUT_NO_STCS   // streaming (evict-first) stores: the outputs are written once and not re-read by the library
+  __device__ __forceinline__ void put(float v) { __stcs(p, v); p += nw; }
+  __device__ __forceinline__ void puti(int v) { __stcs((int*)p, v); p += nw; }
+#else
+  __device__ __forceinline__ void put(float v) { *p = v; p += nw; }
+  __device__ __forceinline__ void puti(int v) { *(int*)p = v; p += nw; }
+#endif
+};
 
 // world pose of an object fixed to frame f: p = x_f + R_f lpos, M = R_f lmat
-__device__ __forceinline__ void framePose(const Ctx& c, const SmemLayout& L, int f, const float* lpos, const float* lmat, float* p, float* M, float* R) {
+template <int STRIDE> __device__ __forceinline__ void framePose(const CtxT<STRIDE>& c, const SmemLayout& L, int f, const float* lpos, const float* lmat, float* p, float* M, float* R) {
   const int o = L.frames + 16 * f;
 #pragma unroll
   for (int k = 0; k < 9; k++) R[k] = S(c, o + 7 + k);
@@ -42,13 +55,20 @@ __device__ __forceinline__ void framePose(const Ctx& c, const SmemLayout& L, int
       for (int j = 0; j < 3; j++) M[3 * i + j] = fmaf(R[3 * i], lmat[j], fmaf(R[3 * i + 1], lmat[3 + j], R[3 * i + 2] * lmat[6 + j]));
 }
 
-__global__ void __launch_bounds__(128, 8) outKernel(int slot, int nworld, int stride, const int* __restrict__ mask, int do_reset,
+#ifndef OUT_THREADS
+#define OUT_THREADS 128
+#endif
+#ifndef OUT_MINBLOCKS
+#define OUT_MINBLOCKS 12
+#endif
+template <int STRIDE>
+__global__ void __launch_bounds__(OUT_THREADS, OUT_MINBLOCKS) outKernel(int slot, int nworld, const int* __restrict__ mask, int do_reset,
                                                  const float* __restrict__ scratch) {
   const DevModel& D = oP[slot].D; const SmemLayout& L = oP[slot].L; const FieldPtrs& F = oP[slot].F;
-  Ctx c; c.w = (size_t)blockIdx.x * 128 + threadIdx.x; c.nw = (size_t)nworld; c.stride = (size_t)stride;
+  CtxT<STRIDE> c; c.w = (size_t)blockIdx.x * OUT_THREADS + threadIdx.x; c.nw = (size_t)nworld;
   if (c.w >= c.nw) return;
   if (do_reset && mask && !mask[c.w]) return;
-  c.sm = scratch + (c.w / c.stride) * (size_t)L.total * c.stride + (c.w % c.stride);
+  c.sm = scratch + (c.w / STRIDE) * (size_t)L.total * STRIDE + (c.w % STRIDE);
   const int nv = D.nv;
   void* sp = F.p[MYO_F_SITE_XPOS]; void* smt = F.p[MYO_F_SITE_XMAT]; void* gp = F.p[MYO_F_GEOM_XPOS]; void* gm = F.p[MYO_F_GEOM_XMAT];
   void* xpos = F.p[MYO_F_XPOS]; void* xquat = F.p[MYO_F_XQUAT]; void* xmat = F.p[MYO_F_XMAT]; void* xipos = F.p[MYO_F_XIPOS];
@@ -69,99 +89,117 @@ __global__ void __launch_bounds__(128, 8) outKernel(int slot, int nworld, int st
             n10 = n9 + (cdo ? nv : 0);
   const int ncon = __float_as_int(S(c, L.counts));
   const int nefc = __float_as_int(S(c, L.counts + 1));   // left by the step kernel: ncon, nefc, niter
+  const size_t nw = c.nw, w = c.w;
   for (int it = blockIdx.y; it < n10; it += gridDim.y) {
-    if (it < n0) {
-      const int q = it;
+    if (it < n1) {   // site or geom pose
+      const bool site = it < n0;
+      const int q = site ? it : it - n0;
+      void* po = site ? sp : gp; void* mo = site ? smt : gm;
       float p[3], M[9], R[9];
-      framePose(c, L, D.site_frame[q], D.site_lpos + 3 * q, D.site_lmat + 9 * q, p, smt ? M : nullptr, R);
-      if (sp) { OF(sp, 3 * q) = p[0]; OF(sp, 3 * q + 1) = p[1]; OF(sp, 3 * q + 2) = p[2]; }
-      if (smt)
+      framePose(c, L, site ? D.site_frame[q] : D.geom_frame[q], (site ? D.site_lpos : D.geom_lpos) + 3 * q, (site ? D.site_lmat : D.geom_lmat) + 9 * q,
+                p, mo ? M : nullptr, R);
+      if (po) { Row o(po, 3 * (size_t)q, nw, w); o.put(p[0]); o.put(p[1]); o.put(p[2]); }
+      if (mo) {
+        Row o(mo, 9 * (size_t)q, nw, w);
 #pragma unroll
-        for (int k = 0; k < 9; k++) OF(smt, 9 * q + k) = M[k];
-    } else if (it < n1) {
-      const int g = it - n0;
-      float p[3], M[9], R[9];
-      framePose(c, L, D.geom_frame[g], D.geom_lpos + 3 * g, D.geom_lmat + 9 * g, p, gm ? M : nullptr, R);
-      if (gp) { OF(gp, 3 * g) = p[0]; OF(gp, 3 * g + 1) = p[1]; OF(gp, 3 * g + 2) = p[2]; }
-      if (gm)
-#pragma unroll
-        for (int k = 0; k < 9; k++) OF(gm, 9 * g + k) = M[k];
+        for (int k = 0; k < 9; k++) o.put(M[k]);
+      }
     } else if (it < n2) {
       const int b = it - n1;
       float p[3], M[9], R[9];
       const int f = D.body_frame[b];
       framePose(c, L, f, D.body_off_pos + 3 * b, D.body_off_mat + 9 * b, p, M, R);
-      if (xpos) { OF(xpos, 3 * b) = p[0]; OF(xpos, 3 * b + 1) = p[1]; OF(xpos, 3 * b + 2) = p[2]; }
+      if (xpos) { Row o(xpos, 3 * (size_t)b, nw, w); o.put(p[0]); o.put(p[1]); o.put(p[2]); }
       if (xquat) {
-        const int o = L.frames + 16 * f + 3;
-        const float aw = S(c, o), ax = S(c, o + 1), ay = S(c, o + 2), az = S(c, o + 3);
+        const int o_ = L.frames + 16 * f + 3;
+        const float aw = S(c, o_), ax = S(c, o_ + 1), ay = S(c, o_ + 2), az = S(c, o_ + 3);
         const float* bq = D.body_off_quat + 4 * b;
         float qw = aw * bq[0] - ax * bq[1] - ay * bq[2] - az * bq[3], qx = aw * bq[1] + ax * bq[0] + ay * bq[3] - az * bq[2],
               qy = aw * bq[2] - ax * bq[3] + ay * bq[0] + az * bq[1], qz = aw * bq[3] + ax * bq[2] - ay * bq[1] + az * bq[0];
         const float n = sqrtf(qw * qw + qx * qx + qy * qy + qz * qz);
         if (n < 1e-15f) { qw = 1.f; qx = qy = qz = 0.f; } else { const float s = 1.f / n; qw *= s; qx *= s; qy *= s; qz *= s; }
-        OF(xquat, 4 * b) = qw; OF(xquat, 4 * b + 1) = qx; OF(xquat, 4 * b + 2) = qy; OF(xquat, 4 * b + 3) = qz;
+        Row o(xquat, 4 * (size_t)b, nw, w); o.put(qw); o.put(qx); o.put(qy); o.put(qz);
       }
-      if (xmat)
+      if (xmat) {
+        Row o(xmat, 9 * (size_t)b, nw, w);
 #pragma unroll
-        for (int k = 0; k < 9; k++) OF(xmat, 9 * b + k) = M[k];
+        for (int k = 0; k < 9; k++) o.put(M[k]);
+      }
       if (xipos) {
         const float* ip = D.body_ipos + 3 * b;
+        Row o(xipos, 3 * (size_t)b, nw, w);
 #pragma unroll
-        for (int i = 0; i < 3; i++) OF(xipos, 3 * b + i) = p[i] + fmaf(M[3 * i], ip[0], fmaf(M[3 * i + 1], ip[1], M[3 * i + 2] * ip[2]));
+        for (int i = 0; i < 3; i++) o.put(p[i] + fmaf(M[3 * i], ip[0], fmaf(M[3 * i + 1], ip[1], M[3 * i + 2] * ip[2])));
       }
       if (ximat) {
         const float* im = D.body_imat + 9 * b;
+        Row o(ximat, 9 * (size_t)b, nw, w);
 #pragma unroll
         for (int i = 0; i < 3; i++)
 #pragma unroll
-          for (int j = 0; j < 3; j++) OF(ximat, 9 * b + 3 * i + j) = fmaf(M[3 * i], im[j], fmaf(M[3 * i + 1], im[3 + j], M[3 * i + 2] * im[6 + j]));
+          for (int j = 0; j < 3; j++) o.put(fmaf(M[3 * i], im[j], fmaf(M[3 * i + 1], im[3 + j], M[3 * i + 2] * im[6 + j])));
       }
-    } else if (it < n3) {   // dense ten_J row = zeros with the sparse entries (sorted by dof) merged in
-      const int k = it - n2;
-      int q = D.ten_nzstart[k];
-      const int qend = D.ten_nzstart[k + 1];
+    } else if (it < n4) {   // dense ten_J / actuator_moment row = zeros with the sparse entries (sorted by dof) merged in
+      const bool isten = it < n3;
+      const int a = isten ? it - n2 : it - n3;
+      int q = 0, qend = 0, jd = -1;
+      float gear = 1.f;
+      if (isten) { q = D.ten_nzstart[a]; qend = D.ten_nzstart[a + 1]; }
+      else {           // the tendon's sparse row scaled by the gear, or the joint's dof
+        const int id = D.act_trnid[a];
+        gear = D.act_gear[a];
+        if (D.act_trntype[a] == 3) { q = D.ten_nzstart[id]; qend = D.ten_nzstart[id + 1]; } else jd = D.jnt_dofadr[id];
+      }
+      Row o(isten ? tj : am, (size_t)a * nv, nw, w);
+      int next = q < qend ? D.nz_dof[q] : -1;
+      const float* src = c.sm + (L.tenJ + q) * STRIDE;
       for (int i = 0; i < nv; i++) {
         float v = 0.f;
-        if (q < qend && D.nz_dof[q] == i) { v = S(c, L.tenJ + q); q++; }
-        OF(tj, k * nv + i) = v;
-      }
-    } else if (it < n4) {   // dense actuator_moment row = the tendon's sparse row scaled by the gear, or the joint's dof
-      const int a = it - n3;
-      const int id = D.act_trnid[a];
-      const bool ten = D.act_trntype[a] == 3;
-      int k = ten ? D.ten_nzstart[id] : 0;
-      const int kend = ten ? D.ten_nzstart[id + 1] : 0;
-      const int jd = ten ? -1 : D.jnt_dofadr[id];
-      const float gear = D.act_gear[a];
-      for (int i = 0; i < nv; i++) {
-        float v = 0.f;
-        if (k < kend && D.nz_dof[k] == i) { v = gear * S(c, L.tenJ + k); k++; }
+        if (i == next) { v = gear * *src; src += STRIDE; q++; next = q < qend ? D.nz_dof[q] : -1; }
         if (i == jd) v = gear;
-        OF(am, a * nv + i) = v;
+        o.put(v);
       }
     } else if (it < n5) {   // dense symmetric qM row: zeros, then the dof's ancestor chain and its descendants
       const int i = it - n4;
-      for (int k = 0; k < nv; k++) OF(qMo, i * nv + k) = 0.f;
+      { Row o(qMo, (size_t)i * nv, nw, w); for (int k = 0; k < nv; k++) o.put(0.f); }
+      float* row = (float*)qMo + (size_t)i * nv * nw + w;
       const int a = D.dof_Madr[i], d = D.dof_rowlen[i];
-      for (int q = 0; q < d; q++) OF(qMo, i * nv + D.M_col[a + q]) = S(c, L.qM + a + q);
-      for (int e = D.desc_start[i]; e < D.desc_start[i + 1]; e++) OF(qMo, i * nv + D.desc_dof[e]) = S(c, L.qM + D.desc_idx[e]);
+      for (int q = 0; q < d; q++) row[(size_t)D.M_col[a + q] * nw] = S(c, L.qM + a + q);
+      for (int e = D.desc_start[i]; e < D.desc_start[i + 1]; e++) row[(size_t)D.desc_dof[e] * nw] = S(c, L.qM + D.desc_idx[e]);
     } else if (it < n6) {   // dense efc_J row from the implied representation (see team.cu "constraints")
       const int r = it - n5;
       const bool on = r < nefc;
       const int njm = D.njmax;
       const int d0 = on ? __float_as_int(S(c, L.efc + E_DESC0 * njm + r)) : 0, type = d0 & 3, id = d0 >> 2;
       const float coef = on ? S(c, L.efc + E_COEF * njm + r) : 0.f;
-      const int t1 = on && type == ROW_CON ? __float_as_int(S(c, L.efc + E_DESC1 * njm + r)) : -1;
-      for (int k = 0; k < nv; k++) {
-        float v = 0.f;
-        if (on) {
-          if (type == ROW_LIMJ) v = D.limj_dof[id] == k ? coef : 0.f;
-          else if (type == ROW_EQ) v = D.eq_dof1[id] == k ? 1.f : (D.eq_dof2[id] == k ? coef : 0.f);
-          else if (type == ROW_CON) v = S(c, L.conJ + id * nv + k) + (t1 >= 0 ? coef * S(c, L.conJ + t1 * nv + k) : 0.f);
-          else { const int tn = D.limt_ten[id]; for (int q = D.ten_nzstart[tn]; q < D.ten_nzstart[tn + 1]; q++) if (D.nz_dof[q] == k) v = coef * S(c, L.tenJ + q); }
+      Row o(eJ, (size_t)r * nv, nw, w);
+      if (!on) { for (int k = 0; k < nv; k++) o.put(0.f); }
+      else if (type == ROW_CON) {
+        const int t1 = __float_as_int(S(c, L.efc + E_DESC1 * njm + r));
+        const float* p0 = c.sm + (L.conJ + id * nv) * STRIDE;
+        if (t1 >= 0) {
+          const float* p1 = c.sm + (L.conJ + t1 * nv) * STRIDE;
+#pragma unroll 4
+          for (int k = 0; k < nv; k++) o.put(p0[k * STRIDE] + coef * p1[k * STRIDE]);
+        } else {
+#pragma unroll 4
+          for (int k = 0; k < nv; k++) o.put(p0[k * STRIDE]);
         }
-        OF(eJ, r * nv + k) = v;
+      } else if (type == ROW_LIMJ) {
+        const int dof = D.limj_dof[id];
+        for (int k = 0; k < nv; k++) o.put(k == dof ? coef : 0.f);
+      } else if (type == ROW_EQ) {
+        const int d1 = D.eq_dof1[id], d2 = D.eq_dof2[id];
+        for (int k = 0; k < nv; k++) o.put(k == d1 ? 1.f : (k == d2 ? coef : 0.f));
+      } else {
+        const int tn = D.limt_ten[id];
+        int q = D.ten_nzstart[tn];
+        const int qend = D.ten_nzstart[tn + 1];
+        for (int k = 0; k < nv; k++) {
+          float v = 0.f;
+          if (q < qend && D.nz_dof[q] == k) { v = coef * S(c, L.tenJ + q); q++; }
+          o.put(v);
+        }
       }
     } else if (it < n7) {   // contact record (padded to nconmax)
       const int q = it - n6;
@@ -169,11 +207,11 @@ __global__ void __launch_bounds__(128, 8) outKernel(int slot, int nworld, int st
       const int cr = L.con + 12 * q;
       const int pr = on ? __float_as_int(S(c, cr + 7)) : 0;
       const float* pp = D.pair_prm + 16 * pr;
-      if (cg) { ((int*)cg)[(size_t)(2 * q) * c.nw + c.w] = on ? D.cg_geom[D.pair_cg1[pr]] : -1; ((int*)cg)[(size_t)(2 * q + 1) * c.nw + c.w] = on ? D.cg_geom[D.pair_cg2[pr]] : -1; }
-      if (cdim) ((int*)cdim)[(size_t)q * c.nw + c.w] = on ? __float_as_int(S(c, cr + 9)) : 0;
-      if (cadr) ((int*)cadr)[(size_t)q * c.nw + c.w] = on ? __float_as_int(S(c, cr + 8)) : -1;
-      if (cdist) OF(cdist, q) = on ? S(c, cr) : 0.f;
-      if (cpos) for (int k = 0; k < 3; k++) OF(cpos, 3 * q + k) = on ? S(c, cr + 1 + k) : 0.f;
+      if (cg) { Row o(cg, 2 * (size_t)q, nw, w); o.puti(on ? D.cg_geom[D.pair_cg1[pr]] : -1); o.puti(on ? D.cg_geom[D.pair_cg2[pr]] : -1); }
+      if (cdim) Row(cdim, q, nw, w).puti(on ? __float_as_int(S(c, cr + 9)) : 0);
+      if (cadr) Row(cadr, q, nw, w).puti(on ? __float_as_int(S(c, cr + 8)) : -1);
+      if (cdist) Row(cdist, q, nw, w).put(on ? S(c, cr) : 0.f);
+      if (cpos) { Row o(cpos, 3 * (size_t)q, nw, w); for (int k = 0; k < 3; k++) o.put(on ? S(c, cr + 1 + k) : 0.f); }
       if (cfr) {
         float n[3] = {0.f, 0.f, 0.f}, y[3] = {0.f, 0.f, 0.f}, z[3] = {0.f, 0.f, 0.f};
         if (on) {   // contact frame: normal, then the tangent basis of team.cu makeFrame
@@ -187,31 +225,36 @@ __global__ void __launch_bounds__(128, 8) outKernel(int slot, int nworld, int st
           y[0] = t[0]; y[1] = t[1]; y[2] = t[2];
           z[0] = n[1] * t[2] - n[2] * t[1]; z[1] = n[2] * t[0] - n[0] * t[2]; z[2] = n[0] * t[1] - n[1] * t[0];
         }
-        for (int k = 0; k < 3; k++) { OF(cfr, 9 * q + k) = n[k]; OF(cfr, 9 * q + 3 + k) = y[k]; OF(cfr, 9 * q + 6 + k) = z[k]; }
+        Row o(cfr, 9 * (size_t)q, nw, w);
+        for (int k = 0; k < 3; k++) o.put(n[k]);
+        for (int k = 0; k < 3; k++) o.put(y[k]);
+        for (int k = 0; k < 3; k++) o.put(z[k]);
       }
-      if (cinc) OF(cinc, q) = on ? pp[0] - pp[1] : 0.f;
-      if (cfri) for (int k = 0; k < 5; k++) OF(cfri, 5 * q + k) = on ? pp[2 + k] : 0.f;
-      if (csr) for (int k = 0; k < 2; k++) OF(csr, 2 * q + k) = on ? pp[7 + k] : 0.f;
-      if (csi) for (int k = 0; k < 5; k++) OF(csi, 5 * q + k) = on ? pp[9 + k] : 0.f;
+      if (cinc) Row(cinc, q, nw, w).put(on ? pp[0] - pp[1] : 0.f);
+      if (cfri) { Row o(cfri, 5 * (size_t)q, nw, w); for (int k = 0; k < 5; k++) o.put(on ? pp[2 + k] : 0.f); }
+      if (csr) { Row o(csr, 2 * (size_t)q, nw, w); for (int k = 0; k < 2; k++) o.put(on ? pp[7 + k] : 0.f); }
+      if (csi) { Row o(csi, 5 * (size_t)q, nw, w); for (int k = 0; k < 5; k++) o.put(on ? pp[9 + k] : 0.f); }
     } else if (it < n8) {   // per-row constraint scalars (padded to njmax)
       const int r = it - n7, njm = D.njmax;
       const bool on = r < nefc;
-      if (epos) OF(epos, r) = on ? S(c, L.efc + E_POS * njm + r) : 0.f;
-      if (emar) OF(emar, r) = on ? S(c, L.efc + E_MARGIN * njm + r) : 0.f;
-      if (eD) OF(eD, r) = on ? S(c, L.efc + E_D * njm + r) : 0.f;
-      if (earef) OF(earef, r) = on ? S(c, L.efc + E_AREF * njm + r) : 0.f;
-      if (efrc) OF(efrc, r) = on ? S(c, L.efc + E_FORCE * njm + r) : 0.f;
+      if (epos) Row(epos, r, nw, w).put(on ? S(c, L.efc + E_POS * njm + r) : 0.f);
+      if (emar) Row(emar, r, nw, w).put(on ? S(c, L.efc + E_MARGIN * njm + r) : 0.f);
+      if (eD) Row(eD, r, nw, w).put(on ? S(c, L.efc + E_D * njm + r) : 0.f);
+      if (earef) Row(earef, r, nw, w).put(on ? S(c, L.efc + E_AREF * njm + r) : 0.f);
+      if (efrc) Row(efrc, r, nw, w).put(on ? S(c, L.efc + E_FORCE * njm + r) : 0.f);
       if (etyp) {
         const int d0 = on ? __float_as_int(S(c, L.efc + E_DESC0 * njm + r)) : 0, type = d0 & 3;
-        ((int*)etyp)[(size_t)r * c.nw + c.w] = !on ? -1 : (type == ROW_EQ ? 0 : (type == ROW_LIMJ ? 3 : (type == ROW_LIMT ? 4 : (__float_as_int(S(c, L.efc + E_DESC1 * njm + r)) < 0 ? 5 : 6))));
+        Row(etyp, r, nw, w).puti(!on ? -1 : (type == ROW_EQ ? 0 : (type == ROW_LIMJ ? 3 : (type == ROW_LIMT ? 4 : (__float_as_int(S(c, L.efc + E_DESC1 * njm + r)) < 0 ? 5 : 6)))));
       }
     } else if (it < n9) {
       const int j = it - n8;
-      if (xa) for (int k = 0; k < 3; k++) OF(xa, 3 * j + k) = S(c, L.xanchor + 3 * j + k);
-      if (xx) for (int k = 0; k < 3; k++) OF(xx, 3 * j + k) = S(c, L.xaxis + 3 * j + k);
+      if (xa) { Row o(xa, 3 * (size_t)j, nw, w); for (int k = 0; k < 3; k++) o.put(S(c, L.xanchor + 3 * j + k)); }
+      if (xx) { Row o(xx, 3 * (size_t)j, nw, w); for (int k = 0; k < 3; k++) o.put(S(c, L.xaxis + 3 * j + k)); }
     } else {
       const int i = it - n9;
-      for (int k = 0; k < 6; k++) OF(cdo, 6 * i + k) = S(c, L.cdof + 6 * i + k);
+      Row o(cdo, 6 * (size_t)i, nw, w);
+#pragma unroll
+      for (int k = 0; k < 6; k++) o.put(S(c, L.cdof + 6 * i + k));
     }
   }
 }
@@ -236,13 +279,21 @@ int myo_out_upload(int slot, const DevModel& D, const SmemLayout& L, const Field
   return cudaMemcpyToSymbolAsync(oP, &P, sizeof(OutParams), (size_t)slot * sizeof(OutParams), cudaMemcpyHostToDevice, (cudaStream_t)stream) == cudaSuccess ? 0 : -1;
 }
 int myo_out_launch(int slot, int nworld, int stride, const int* reset_mask, int do_reset, const float* scratch, void* stream) {
-  dim3 grid((nworld + 127) / 128, 1);
-  // 8 CTAs are resident per SM (64 registers); many short CTAs (8 waves) let the hardware scheduler even out the item costs
+  dim3 grid((nworld + OUT_THREADS - 1) / OUT_THREADS, 1);
+  // OUT_MINBLOCKS CTAs are resident per SM; many short CTAs (8 waves) let the hardware scheduler even out the item costs
   static const int want_env = getenv("MYO_OUT_BLOCKS") ? atoi(getenv("MYO_OUT_BLOCKS")) : 0;   // developer knob
-  const int want = want_env > 0 ? want_env : 148 * 8 * 8;
+  const int want = want_env > 0 ? want_env : 148 * OUT_MINBLOCKS * 8;
   grid.y = (unsigned)((want + grid.x - 1) / grid.x);
   if (grid.y < 1) grid.y = 1;
   if (grid.y > 512) grid.y = 512;
-  outKernel<<<grid, 128, 0, (cudaStream_t)stream>>>(slot, nworld, stride, reset_mask, do_reset, scratch);
+  cudaStream_t st = (cudaStream_t)stream;
+  switch (stride) {
+    case 32: outKernel<32><<<grid, OUT_THREADS, 0, st>>>(slot, nworld, reset_mask, do_reset, scratch); break;
+    case 16: outKernel<16><<<grid, OUT_THREADS, 0, st>>>(slot, nworld, reset_mask, do_reset, scratch); break;
+    case 8: outKernel<8><<<grid, OUT_THREADS, 0, st>>>(slot, nworld, reset_mask, do_reset, scratch); break;
+    case 4: outKernel<4><<<grid, OUT_THREADS, 0, st>>>(slot, nworld, reset_mask, do_reset, scratch); break;
+    case 2: outKernel<2><<<grid, OUT_THREADS, 0, st>>>(slot, nworld, reset_mask, do_reset, scratch); break;
+    default: return -1;
+  }
   return cudaPeekAtLastError() == cudaSuccess ? 0 : -1;
 }

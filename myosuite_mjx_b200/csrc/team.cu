@@ -1853,7 +1853,9 @@ __device__ __forceinline__ void forwardWorld(int slot, int fslot, SP sm, Tm t, W
     TSYNC();
   }
   if (live && t.tl == 0) { sm[L.counts] = __int_as_float(ncon); sm[L.counts + 1] = __int_as_float(nefc); sm[L.counts + 2] = __int_as_float(niter); }
+#ifndef NO_SYNC_AFTER_NEWTON
   PHASE_SYNC();
+#endif
   *ncon_o = ncon; *nefc_o = nefc; *niter_o = niter;
 }
 
@@ -1966,7 +1968,9 @@ __global__ void __launch_bounds__(32 * CTA_WARPS, CTA_MINBLOCKS) stepKernel(int 
     time += h;
     TSYNC();
     }
+#ifndef NO_SYNC_AFTER_EULER
     PHASE_SYNC();
+#endif
   }
   // ---- state out
   if (!live) return;
