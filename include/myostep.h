@@ -203,6 +203,17 @@ int myo_batch_bind(myo_batch *b, int field, void *dev_ptr, int64_t nbytes);
  * myosuite/mjx/myodm_v0.py:159): all outputs from the bound state, state not advanced. */
 int myo_forward(myo_batch *b, void *cuda_stream);
 
+/* mj_forward on the worlds whose mask entry is non-zero only (NULL = all); the others are not touched. */
+int myo_forward_masked(myo_batch *b, const int32_t *world_mask_dev, void *cuda_stream);
+
+/* mj_step1-style refresh of the masked worlds (NULL = all): the position- and velocity-dependent fields (kinematics, com,
+ * tendon lengths / moment arms / velocities, actuator_length / actuator_velocity, cvel, cdof_dot, qfrc_bias, qfrc_passive)
+ * are recomputed from the current state; contacts, constraint rows, actuator_force, qacc and the warm start keep the values
+ * of the last full pass.  This is what the classic path's observations see: dm_control's Physics.step finishes with
+ * mj_step1 after the last mj_step (reference: self.sim.step(substeps), myosuite/physics/mj_sim_scene.py:55), so xpos,
+ * xipos, cvel, actuator_length ... describe the NEW state while actuator_force is the last step's. */
+int myo_forward_posvel(myo_batch *b, const int32_t *world_mask_dev, void *cuda_stream);
+
 /* nsubsteps x mj_step on every world with ctrl held (reference: jit_step at myosuite/mjx/play.py:47;
  * sim.advance(substeps=n_frames) at myosuite/robot/robot.py:880-882; pipeline_step at myodm_v0.py:287).
  * Output fields describe the last substep's forward pass, as mjData does after mj_step. */
@@ -233,10 +244,20 @@ int myo_step_host(myo_batch *b, int nsubsteps, const float *qpos, const float *q
  * sequence does not depend on the batch size or on the number of GPUs.  All env buffers are caller-owned device
  * memory in the [k][nworld] layout, bound with myo_env_bind. */
 enum { MYO_COND_NONE = 0, MYO_COND_SARCOPENIA = 1, MYO_COND_FATIGUE = 2, MYO_COND_REAFFERENTATION = 3 };
-enum { MYO_OBS_TIME = 0, MYO_OBS_QPOS = 1, MYO_OBS_QVEL = 2, MYO_OBS_ACT = 3, MYO_OBS_POSE_ERR = 4 };   /* obs_dict keys */
+enum { MYO_ENV_POSE = 0, MYO_ENV_WALK = 1 };   /* PoseEnvV0 (pose_v0.py) / WalkEnvV0 (walk_v0.py) */
+enum {   /* obs_dict keys: pose_v0.py:106-116, walk_v0.py:263-283 */
+  MYO_OBS_TIME = 0, MYO_OBS_QPOS = 1, MYO_OBS_QVEL = 2, MYO_OBS_ACT = 3, MYO_OBS_POSE_ERR = 4,
+  MYO_OBS_QPOS_WITHOUT_XY = 5, MYO_OBS_COM_VEL = 6, MYO_OBS_TORSO_ANGLE = 7, MYO_OBS_FEET_HEIGHTS = 8, MYO_OBS_HEIGHT = 9,
+  MYO_OBS_FEET_REL_POSITIONS = 10, MYO_OBS_PHASE_VAR = 11, MYO_OBS_MUSCLE_LENGTH = 12, MYO_OBS_MUSCLE_VELOCITY = 13,
+  MYO_OBS_MUSCLE_FORCE = 14
+};
+#define MYO_MAX_OBS_KEYS 16
 enum { MYO_TARGET_FIXED = 0, MYO_TARGET_GENERATE = 1 };
 enum { MYO_RESET_INIT = 0, MYO_RESET_RANDOM = 1 };
-enum { MYO_RWD_POSE = 0, MYO_RWD_BONUS, MYO_RWD_PENALTY, MYO_RWD_ACT_REG, MYO_RWD_SPARSE, MYO_RWD_SOLVED, MYO_RWD_COUNT };
+/* slots of MYO_E_RWD_TERMS.  pose: pose, bonus, penalty, act_reg, sparse, solved, done, -.
+ * walk (walk_v0.py:297-310): vel_reward, cyclic_hip, ref_rot, joint_angle_rew, act_mag, sparse, solved, done. */
+enum { MYO_RWD_POSE = 0, MYO_RWD_BONUS, MYO_RWD_PENALTY, MYO_RWD_ACT_REG, MYO_RWD_SPARSE, MYO_RWD_SOLVED, MYO_RWD_DONE, MYO_RWD_SPARE, MYO_RWD_COUNT };
+enum { MYO_RWD_W_VEL = 0, MYO_RWD_W_CYCLIC_HIP, MYO_RWD_W_REF_ROT, MYO_RWD_W_JOINT_ANGLE, MYO_RWD_W_ACT_MAG, MYO_RWD_W_SPARSE, MYO_RWD_W_SOLVED, MYO_RWD_W_DONE };
 
 typedef enum myo_env_field {
   MYO_E_ACTION = 0,   /* [nu]            input of myo_env_step */
@@ -254,7 +275,7 @@ typedef enum myo_env_field {
 /* host arrays; copied at myo_env_create */
 typedef struct myo_env_desc {
   int32_t frame_skip, normalize_act, muscle_condition, epl_id, eip_id;
-  int32_t nobs_keys, obs_keys[8];
+  int32_t nobs_keys, obs_keys[MYO_MAX_OBS_KEYS];
   int32_t ntarget, target_type, reset_type, auto_reset, horizon, world_offset;
   uint64_t seed;
   float pose_thd, far_th, w_pose, w_bonus, w_act_reg, w_penalty;
@@ -267,6 +288,16 @@ typedef struct myo_env_desc {
   const int32_t *act_is_muscle;              /* [nu] actuator_dyntype == mjDYN_MUSCLE */
   const float *ctrl_lo, *ctrl_hi;            /* [nu] actuator_ctrlrange */
   const float *tau_act, *tau_deact;          /* [nu] actuator_dynprm[:,0], [:,1] */
+  /* ---- kind == MYO_ENV_WALK (myosuite/envs/myo/myobase/walk_v0.py:229-257 setup, :263-310 obs / reward, :312-350 reset,
+   * :352-478 helpers).  Needs the fields xpos, xquat, xipos, cvel, actuator_length / velocity / force bound on the batch. */
+  int32_t kind;
+  int32_t foot_l_bid, foot_r_bid, pelvis_bid, torso_bid;   /* talus_l, talus_r, pelvis, torso */
+  int32_t hip_flex_adr[2];                                 /* qpos address of hip_flexion_l, hip_flexion_r */
+  int32_t hip_angle_adr[4];                                /* hip_adduction_l / _r, hip_rotation_l / _r */
+  float min_height, max_rot, hip_period, target_x_vel, target_y_vel, target_rot[4], reset_noise;
+  float w_vel, w_done, w_cyclic, w_ref_rot, w_joint_angle;
+  const float *body_mass;                                  /* [nbody] */
+  const float *alt_qpos, *alt_qvel;                        /* [nq], [nv]: second start state of reset_type random (key 3) */
 } myo_env_desc;
 
 typedef struct myo_env myo_env;
@@ -278,7 +309,9 @@ int myo_env_seed(myo_env *e, uint64_t seed);
 /* reset the masked worlds (NULL = all): new target, new initial state, zero reward / done, fresh observation.
  * Derived mjData fields are refreshed by the next step (call myo_forward for them earlier). */
 int myo_env_reset(myo_env *e, const int32_t *world_mask_dev, void *cuda_stream);
-/* one env step of every world: pre kernel, frame_skip fused mj_steps, post kernel (3 or 4 launches, no sync) */
+/* one env step of every world: pre kernel, frame_skip fused mj_steps, post kernel (3 or 4 launches, no sync).
+ * The walk env adds the refresh of the position / velocity fields its observation reads (myo_forward_posvel) and a
+ * masked mj_forward of the worlds it reset. */
 int myo_env_step(myo_env *e, void *cuda_stream);
 /* MujocoEnv.forward (obs + reward terms + done from the CURRENT state; no physics, no counters, no reset):
  * what the reference evaluates after reset and after every step (myosuite/envs/myo/base_v0.py:120). */

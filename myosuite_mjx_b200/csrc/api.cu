@@ -207,7 +207,7 @@ static int launch(myo_batch* b, int nsub, int forward_only, const int32_t* mask,
     return fail(MYO_ERR_CUDA, std::string("kernel launch failed: ") + cudaGetErrorString(cudaGetLastError()));
   if (b->wide) {
     g_launches++;
-    if (myo_out_launch(b->slot, b->nworld, 32 / b->kern->team, mask, do_reset, b->scratch, stream) != 0)
+    if (myo_out_launch(b->slot, b->nworld, 32 / b->kern->team, mask, forward_only == 2, b->scratch, stream) != 0)
       return fail(MYO_ERR_CUDA, std::string("kernel launch failed: ") + cudaGetErrorString(cudaGetLastError()));
   }
   return MYO_OK;
@@ -218,6 +218,8 @@ int myo_step(myo_batch* b, int nsubsteps, void* stream) {
   return launch(b, nsubsteps, 0, nullptr, 0, stream);
 }
 int myo_reset(myo_batch* b, const int32_t* world_mask_dev, void* stream) { return launch(b, 0, 1, world_mask_dev, 1, stream); }
+int myo_forward_masked(myo_batch* b, const int32_t* world_mask_dev, void* stream) { return launch(b, 0, 1, world_mask_dev, 0, stream); }
+int myo_forward_posvel(myo_batch* b, const int32_t* world_mask_dev, void* stream) { return launch(b, 0, 2, world_mask_dev, 0, stream); }
 
 int myo_step_host(myo_batch* b, int nsubsteps, const float* qpos, const float* qvel, const float* act, const float* ctrl,
                   float* qpos_out, float* qvel_out, float* act_out, void* stream) {

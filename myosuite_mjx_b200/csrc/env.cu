@@ -19,17 +19,23 @@ struct EnvTables {   // device copies of the myo_env_desc arrays
   const int* target_qposadr; const float *target_range, *target_value, *init_qpos, *init_qvel, *reset_lo, *reset_hi;
   const int* act_is_muscle; const int* muscle_slot;   // muscle_slot[a]: index among the muscle actuators, -1 otherwise
   const float *ctrl_lo, *ctrl_hi, *tau_act, *tau_deact;
+  const float *body_mass, *alt_qpos, *alt_qvel;   // walk
 };
 struct EnvParams {
   int nworld, nq, nv, na, nu, nmuscle;
   int frame_skip, normalize_act, cond, epl, eip;
-  int nobs_keys, obs_keys[8], nobs;
+  int nobs_keys, obs_keys[MYO_MAX_OBS_KEYS], nobs;
   int ntarget, target_type, reset_type, auto_reset, horizon, world_offset;
   unsigned long long seed;
   float dt, pose_thd, far_th, w_pose, w_bonus, w_act_reg, w_penalty, fat_F, fat_R, fat_r;
   EnvTables T;
   void* E[MYO_E_COUNT];   // env buffers
   float *qpos, *qvel, *act, *ctrl, *time, *warm; int* status;   // bound state fields of the batch
+  // walk env
+  int kind, nbody, foot_l, foot_r, pelvis, torso, hip_flex[2], hip_angle[4];
+  float min_height, max_rot, hip_period, target_x_vel, target_y_vel, target_rot[4], reset_noise, w_vel, w_done, w_cyclic, w_ref_rot, w_joint_angle;
+  const float *xpos, *xquat, *xipos, *cvel, *actlen, *actvel, *actfrc;   // bound derived fields the walk observation reads
+  int* reset_mask;   // [nworld], library-owned: worlds reset by the last step (they need a full mj_forward)
 };
 
 struct myo_env {
@@ -108,15 +114,32 @@ __device__ void envResetWorld(const EnvParams& P, size_t w) {
     } else t = P.T.target_value[k];
     EF(MYO_E_TARGET, k) = t;
   }
-  for (int j = 0; j < P.nq; j++) {
-    float q = P.T.init_qpos[j];
-    if (P.reset_type == MYO_RESET_RANDOM) {
-      const float lo = P.T.reset_lo[j], hi = P.T.reset_hi[j];
-      q = __fadd_rn(lo, __fmul_rn(hi - lo, envUniform(P.seed, gw, ep, 1u, (unsigned)j)));
+  if (P.kind == MYO_ENV_WALK) {
+    // walk_v0.py:312-350: "random" starts from one of two keyframes (left or right knee flexed) plus N(0, 0.02) noise on
+    // every coordinate but the root height and orientation; otherwise the given start state
+    const bool alt = P.reset_type == MYO_RESET_RANDOM && !(envUniform(P.seed, gw, ep, 2u, 0u) < 0.5f);
+    const float* q0 = alt ? P.T.alt_qpos : P.T.init_qpos;
+    const float* v0 = alt ? P.T.alt_qvel : P.T.init_qvel;
+    for (int j = 0; j < P.nq; j++) {
+      float q = q0[j];
+      if (P.reset_type == MYO_RESET_RANDOM && !(j >= 2 && j < 7)) {
+        const float u1 = 1.0f - envUniform(P.seed, gw, ep, 3u, (unsigned)j), u2 = envUniform(P.seed, gw, ep, 4u, (unsigned)j);
+        q += P.reset_noise * sqrtf(-2.0f * logf(u1)) * cosf(6.2831853071795865f * u2);   // Box-Muller
+      }
+      ST(P.qpos, j) = q;
     }
-    ST(P.qpos, j) = q;
+    for (int j = 0; j < P.nv; j++) { ST(P.qvel, j) = v0[j]; ST(P.warm, j) = 0.f; }
+  } else {
+    for (int j = 0; j < P.nq; j++) {
+      float q = P.T.init_qpos[j];
+      if (P.reset_type == MYO_RESET_RANDOM) {
+        const float lo = P.T.reset_lo[j], hi = P.T.reset_hi[j];
+        q = __fadd_rn(lo, __fmul_rn(hi - lo, envUniform(P.seed, gw, ep, 1u, (unsigned)j)));
+      }
+      ST(P.qpos, j) = q;
+    }
+    for (int j = 0; j < P.nv; j++) { ST(P.qvel, j) = P.T.init_qvel[j]; ST(P.warm, j) = 0.f; }
   }
-  for (int j = 0; j < P.nv; j++) { ST(P.qvel, j) = P.T.init_qvel[j]; ST(P.warm, j) = 0.f; }
   for (int j = 0; j < P.na; j++) ST(P.act, j) = 0.f;
   for (int j = 0; j < P.nu; j++) ST(P.ctrl, j) = 0.f;
   ST(P.time, 0) = 0.f;
@@ -126,6 +149,19 @@ __device__ void envResetWorld(const EnvParams& P, size_t w) {
   EI(MYO_E_STEPS, 0) = 0;
   EI(MYO_E_EPISODE, 0) = (int)(ep + 1u);
 }
+
+// walk_v0.py:436-478: mass-weighted centre-of-mass velocity (x, y of -cvel's linear part) and height (z of xipos)
+__device__ void walkCom(const EnvParams& P, size_t w, float* vx, float* vy, float* h) {
+  const size_t nw = (size_t)P.nworld;
+  float sx = 0.f, sy = 0.f, sz = 0.f, sm_ = 0.f;
+  for (int b = 0; b < P.nbody; b++) {
+    const float m = P.T.body_mass[b];
+    sx = fmaf(m, -ST(P.cvel, 6 * b + 3), sx); sy = fmaf(m, -ST(P.cvel, 6 * b + 4), sy); sz = fmaf(m, ST(P.xipos, 3 * b + 2), sz);
+    sm_ += m;
+  }
+  *vx = sx / sm_; *vy = sy / sm_; *h = sz / sm_;
+}
+__device__ __forceinline__ float walkPhase(const EnvParams& P, int steps) { const float x = (float)steps / P.hip_period; return x - floorf(x); }
 
 // obs vector from the state (pose_v0.py:98-116): concatenation of the obs_keys entries
 __device__ void envWriteObs(const EnvParams& P, size_t w) {
@@ -141,6 +177,20 @@ __device__ void envWriteObs(const EnvParams& P, size_t w) {
         else { for (int j = 0; j < P.nq; j++) EF(MYO_E_OBS, o++) = 0.f; }   // pose_v0.py:108-112: zeros_like(qpos)
         break;
       case MYO_OBS_POSE_ERR: for (int k = 0; k < P.ntarget; k++) EF(MYO_E_OBS, o++) = EF(MYO_E_TARGET, k) - ST(P.qpos, P.T.target_qposadr[k]); break;
+      // ---- walk_v0.py:263-283
+      case MYO_OBS_QPOS_WITHOUT_XY: for (int j = 2; j < P.nq; j++) EF(MYO_E_OBS, o++) = ST(P.qpos, j); break;
+      case MYO_OBS_COM_VEL: { float vx, vy, h; walkCom(P, w, &vx, &vy, &h); EF(MYO_E_OBS, o++) = vx; EF(MYO_E_OBS, o++) = vy; } break;
+      case MYO_OBS_TORSO_ANGLE: for (int k = 0; k < 4; k++) EF(MYO_E_OBS, o++) = ST(P.xquat, 4 * P.torso + k); break;
+      case MYO_OBS_FEET_HEIGHTS: EF(MYO_E_OBS, o++) = ST(P.xpos, 3 * P.foot_l + 2); EF(MYO_E_OBS, o++) = ST(P.xpos, 3 * P.foot_r + 2); break;
+      case MYO_OBS_HEIGHT: { float vx, vy, h; walkCom(P, w, &vx, &vy, &h); EF(MYO_E_OBS, o++) = h; } break;
+      case MYO_OBS_FEET_REL_POSITIONS:
+        for (int k = 0; k < 3; k++) EF(MYO_E_OBS, o++) = ST(P.xpos, 3 * P.foot_l + k) - ST(P.xpos, 3 * P.pelvis + k);
+        for (int k = 0; k < 3; k++) EF(MYO_E_OBS, o++) = ST(P.xpos, 3 * P.foot_r + k) - ST(P.xpos, 3 * P.pelvis + k);
+        break;
+      case MYO_OBS_PHASE_VAR: EF(MYO_E_OBS, o++) = walkPhase(P, max(EI(MYO_E_STEPS, 0) - 1, 0)); break;   // self.steps lags the step count by one (walk_v0.py:335-338)
+      case MYO_OBS_MUSCLE_LENGTH: for (int j = 0; j < P.nu; j++) EF(MYO_E_OBS, o++) = ST(P.actlen, j); break;
+      case MYO_OBS_MUSCLE_VELOCITY: for (int j = 0; j < P.nu; j++) EF(MYO_E_OBS, o++) = fminf(fmaxf(ST(P.actvel, j), -100.f), 100.f); break;
+      case MYO_OBS_MUSCLE_FORCE: for (int j = 0; j < P.nu; j++) EF(MYO_E_OBS, o++) = fminf(fmaxf(ST(P.actfrc, j) / 1000.f, -100.f), 100.f); break;
     }
   }
 }
@@ -163,6 +213,7 @@ __global__ void __launch_bounds__(128) envPostKernel(const EnvParams P, const in
   EF(MYO_E_RWD_TERMS, MYO_RWD_POSE) = pose; EF(MYO_E_RWD_TERMS, MYO_RWD_BONUS) = bonus; EF(MYO_E_RWD_TERMS, MYO_RWD_PENALTY) = penalty;
   EF(MYO_E_RWD_TERMS, MYO_RWD_ACT_REG) = act_reg; EF(MYO_E_RWD_TERMS, MYO_RWD_SPARSE) = -dist;
   EF(MYO_E_RWD_TERMS, MYO_RWD_SOLVED) = dist < P.pose_thd ? 1.f : 0.f;
+  EF(MYO_E_RWD_TERMS, MYO_RWD_DONE) = done ? 1.f : 0.f; EF(MYO_E_RWD_TERMS, MYO_RWD_SPARE) = 0.f;
   // dense = sum over rwd_keys_wt in its dict order: pose, bonus, act_reg, penalty (pose_v0.py:16-21,134-136)
   EF(MYO_E_REWARD, 0) = ((P.w_pose * pose + P.w_bonus * bonus) + P.w_act_reg * act_reg) + P.w_penalty * penalty;
   const int steps = EI(MYO_E_STEPS, 0) + advance;
@@ -170,6 +221,55 @@ __global__ void __launch_bounds__(128) envPostKernel(const EnvParams P, const in
   const bool ended = done || (P.horizon > 0 && steps >= P.horizon);
   EF(MYO_E_DONE, 0) = ended ? 1.f : 0.f;
   if (ended && advance && P.auto_reset) envResetWorld(P, w);
+  envWriteObs(P, w);
+}
+
+// ---- walk: reward terms, done, reset decision (walk_v0.py:285-310, 357-478); one thread per world.  Runs after the
+// position / velocity refresh, so xipos, cvel and qpos describe the stepped state as they do on the classic path.
+__global__ void __launch_bounds__(128) envWalkRewardKernel(const EnvParams P, const int advance) {
+  const size_t nw = (size_t)P.nworld;
+  const size_t w = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (w >= nw) return;
+  const int steps0 = EI(MYO_E_STEPS, 0);               // the reference's self.steps while it evaluates this step's reward
+  float vx, vy, height;
+  walkCom(P, w, &vx, &vy, &height);
+  const float ey = P.target_y_vel - vy, ex = P.target_x_vel - vx;
+  const float vel_reward = expf(-(ey * ey)) + expf(-(ex * ex));
+  const float ph = walkPhase(P, advance ? steps0 : max(steps0 - 1, 0));
+  const float twopi = 6.2831853071795865f;
+  const float d0 = 0.8f * cosf(ph * twopi + 3.14159265358979324f) - ST(P.qpos, P.hip_flex[0]), d1 = 0.8f * cosf(ph * twopi) - ST(P.qpos, P.hip_flex[1]);
+  const float cyclic = sqrtf(d0 * d0 + d1 * d1);
+  float r2 = 0.f;
+  for (int k = 0; k < 4; k++) { const float e = 5.0f * (ST(P.qpos, 3 + k) - P.target_rot[k]); r2 = fmaf(e, e, r2); }
+  const float ref_rot = expf(-sqrtf(r2));
+  float mag = 0.f;
+  for (int k = 0; k < 4; k++) mag += fabsf(ST(P.qpos, P.hip_angle[k]));
+  const float joint_angle = expf(-5.0f * (mag * 0.25f));
+  float a2 = 0.f;
+  for (int j = 0; j < P.na; j++) { const float a = ST(P.act, j); a2 = fmaf(a, a, a2); }
+  const float act_mag = P.na != 0 ? sqrtf(a2) / (float)P.na : 0.f;
+  // done: centre of mass too low, or the root frame's x axis turned away (quat2mat(q)[0, 0], myosuite/utils/quat_math.py:160-183)
+  const float qw = ST(P.qpos, 3), qx = ST(P.qpos, 4), qy = ST(P.qpos, 5), qz = ST(P.qpos, 6);
+  const float Nq = qw * qw + qx * qx + qy * qy + qz * qz;
+  const float r00 = Nq > 2.220446049250313e-16f ? 1.0f - (qy * (qy * (2.0f / Nq)) + qz * (qz * (2.0f / Nq))) : 1.0f;
+  const bool done = height < P.min_height || fabsf(r00) > P.max_rot;
+  EF(MYO_E_RWD_TERMS, MYO_RWD_W_VEL) = vel_reward; EF(MYO_E_RWD_TERMS, MYO_RWD_W_CYCLIC_HIP) = cyclic; EF(MYO_E_RWD_TERMS, MYO_RWD_W_REF_ROT) = ref_rot;
+  EF(MYO_E_RWD_TERMS, MYO_RWD_W_JOINT_ANGLE) = joint_angle; EF(MYO_E_RWD_TERMS, MYO_RWD_W_ACT_MAG) = act_mag;
+  EF(MYO_E_RWD_TERMS, MYO_RWD_W_SPARSE) = vel_reward; EF(MYO_E_RWD_TERMS, MYO_RWD_W_SOLVED) = vel_reward >= 1.0f ? 1.f : 0.f;
+  EF(MYO_E_RWD_TERMS, MYO_RWD_W_DONE) = done ? 1.f : 0.f;
+  // dense in the order of DEFAULT_RWD_KEYS_AND_WEIGHTS (walk_v0.py:200-206): vel_reward, done, cyclic_hip, ref_rot, joint_angle_rew
+  EF(MYO_E_REWARD, 0) = (((P.w_vel * vel_reward + P.w_done * (done ? 1.f : 0.f)) + P.w_cyclic * cyclic) + P.w_ref_rot * ref_rot) + P.w_joint_angle * joint_angle;
+  const int steps = steps0 + advance;
+  if (advance) EI(MYO_E_STEPS, 0) = steps;
+  const bool ended = done || (P.horizon > 0 && steps >= P.horizon);
+  EF(MYO_E_DONE, 0) = ended ? 1.f : 0.f;
+  const bool reset = ended && advance && P.auto_reset;
+  if (reset) envResetWorld(P, w);
+  if (P.reset_mask) P.reset_mask[w] = reset ? 1 : 0;
+}
+__global__ void __launch_bounds__(128) envObsKernel(const EnvParams P) {
+  const size_t w = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (w >= (size_t)P.nworld) return;
   envWriteObs(P, w);
 }
 
@@ -181,7 +281,7 @@ __global__ void __launch_bounds__(128) envResetKernel(const EnvParams P, const i
   envResetWorld(P, w);
   EF(MYO_E_REWARD, 0) = 0.f; EF(MYO_E_DONE, 0) = 0.f;
   for (int k = 0; k < MYO_RWD_COUNT; k++) EF(MYO_E_RWD_TERMS, k) = 0.f;
-  envWriteObs(P, w);
+  if (P.kind == MYO_ENV_POSE) envWriteObs(P, w);   // the walk observation needs mj_forward of the new state first
 }
 
 template <class T> const T* toDevice(const T* host, size_t n, std::vector<void*>& owned) {
@@ -211,12 +311,22 @@ int myo_env_create(myo_batch* b, const myo_env_desc* d, myo_env** out) {
   if (!b || !d || !out) return myo_fail(MYO_ERR_ARG, "bad argument");
   const DevModel& D = b->D;
   if (d->frame_skip < 1) return myo_fail(MYO_ERR_ARG, "frame_skip must be >= 1");
-  if (d->nobs_keys < 0 || d->nobs_keys > 8) return myo_fail(MYO_ERR_ARG, "at most 8 obs keys");
+  if (d->nobs_keys < 0 || d->nobs_keys > MYO_MAX_OBS_KEYS) return myo_fail(MYO_ERR_ARG, "too many obs keys");
+  if (d->kind != MYO_ENV_POSE && d->kind != MYO_ENV_WALK) return myo_fail(MYO_ERR_ARG, "unknown env kind");
+  if (d->kind == MYO_ENV_WALK) {
+    if (D.nq < 7 || !d->body_mass) return myo_fail(MYO_ERR_ARG, "the walk env needs a free root joint and body_mass");
+    if (d->reset_type == MYO_RESET_RANDOM && (!d->alt_qpos || !d->alt_qvel)) return myo_fail(MYO_ERR_ARG, "alt_qpos / alt_qvel missing");
+    const int bids[4] = {d->foot_l_bid, d->foot_r_bid, d->pelvis_bid, d->torso_bid};
+    for (int k = 0; k < 4; k++) if (bids[k] < 0 || bids[k] >= D.nbody) return myo_fail(MYO_ERR_ARG, "walk body id out of range");
+    for (int k = 0; k < 2; k++) if (d->hip_flex_adr[k] < 0 || d->hip_flex_adr[k] >= D.nq) return myo_fail(MYO_ERR_ARG, "hip_flex_adr out of range");
+    for (int k = 0; k < 4; k++) if (d->hip_angle_adr[k] < 0 || d->hip_angle_adr[k] >= D.nq) return myo_fail(MYO_ERR_ARG, "hip_angle_adr out of range");
+    if (!(d->hip_period > 0.f)) return myo_fail(MYO_ERR_ARG, "hip_period must be positive");
+  }
   if (d->ntarget < 0 || (d->ntarget > 0 && !d->target_qposadr)) return myo_fail(MYO_ERR_ARG, "target_qposadr missing");
   if (d->target_type == MYO_TARGET_GENERATE && d->ntarget > 0 && !d->target_range) return myo_fail(MYO_ERR_ARG, "target_range missing");
   if (d->target_type == MYO_TARGET_FIXED && d->ntarget > 0 && !d->target_value) return myo_fail(MYO_ERR_ARG, "target_value missing");
   if (!d->init_qpos || !d->init_qvel) return myo_fail(MYO_ERR_ARG, "init_qpos / init_qvel missing");
-  if (d->reset_type == MYO_RESET_RANDOM && (!d->reset_lo || !d->reset_hi)) return myo_fail(MYO_ERR_ARG, "reset range missing");
+  if (d->kind == MYO_ENV_POSE && d->reset_type == MYO_RESET_RANDOM && (!d->reset_lo || !d->reset_hi)) return myo_fail(MYO_ERR_ARG, "reset range missing");
   if (D.nu > 0 && (!d->act_is_muscle || !d->ctrl_lo || !d->ctrl_hi)) return myo_fail(MYO_ERR_ARG, "actuator tables missing");
   if (d->muscle_condition == MYO_COND_FATIGUE && (!d->tau_act || !d->tau_deact)) return myo_fail(MYO_ERR_ARG, "tau_act / tau_deact missing");
   if (d->muscle_condition == MYO_COND_REAFFERENTATION && (d->epl_id < 0 || d->epl_id >= D.nu || d->eip_id < 0 || d->eip_id >= D.nu))
@@ -235,15 +345,29 @@ int myo_env_create(myo_batch* b, const myo_env_desc* d, myo_env** out) {
   P.dt = D.timestep * (float)d->frame_skip;
   P.pose_thd = d->pose_thd; P.far_th = d->far_th; P.w_pose = d->w_pose; P.w_bonus = d->w_bonus; P.w_act_reg = d->w_act_reg; P.w_penalty = d->w_penalty;
   P.fat_F = d->fatigue_F; P.fat_R = d->fatigue_R; P.fat_r = d->fatigue_r;
+  P.kind = d->kind; P.nbody = D.nbody;
+  P.foot_l = d->foot_l_bid; P.foot_r = d->foot_r_bid; P.pelvis = d->pelvis_bid; P.torso = d->torso_bid;
+  for (int k = 0; k < 2; k++) P.hip_flex[k] = d->hip_flex_adr[k];
+  for (int k = 0; k < 4; k++) { P.hip_angle[k] = d->hip_angle_adr[k]; P.target_rot[k] = d->target_rot[k]; }
+  P.min_height = d->min_height; P.max_rot = d->max_rot; P.hip_period = d->hip_period; P.target_x_vel = d->target_x_vel; P.target_y_vel = d->target_y_vel;
+  P.reset_noise = d->reset_noise; P.w_vel = d->w_vel; P.w_done = d->w_done; P.w_cyclic = d->w_cyclic; P.w_ref_rot = d->w_ref_rot; P.w_joint_angle = d->w_joint_angle;
   for (int q = 0; q < d->nobs_keys; q++) {
     const int key = d->obs_keys[q];
     P.obs_keys[q] = key;
+    if (key >= MYO_OBS_QPOS_WITHOUT_XY && d->kind != MYO_ENV_WALK) { delete e; return myo_fail(MYO_ERR_ARG, "walk obs key on a pose env"); }
+    if (key == MYO_OBS_POSE_ERR && d->kind != MYO_ENV_POSE) { delete e; return myo_fail(MYO_ERR_ARG, "pose obs key on a walk env"); }
     switch (key) {
       case MYO_OBS_TIME: P.nobs += 1; break;
       case MYO_OBS_QPOS: P.nobs += D.nq; break;
       case MYO_OBS_QVEL: P.nobs += D.nv; break;
       case MYO_OBS_ACT: P.nobs += D.na > 0 ? D.na : D.nq; break;
       case MYO_OBS_POSE_ERR: P.nobs += d->ntarget; break;
+      case MYO_OBS_QPOS_WITHOUT_XY: P.nobs += D.nq - 2; break;
+      case MYO_OBS_COM_VEL: case MYO_OBS_FEET_HEIGHTS: P.nobs += 2; break;
+      case MYO_OBS_TORSO_ANGLE: P.nobs += 4; break;
+      case MYO_OBS_HEIGHT: case MYO_OBS_PHASE_VAR: P.nobs += 1; break;
+      case MYO_OBS_FEET_REL_POSITIONS: P.nobs += 6; break;
+      case MYO_OBS_MUSCLE_LENGTH: case MYO_OBS_MUSCLE_VELOCITY: case MYO_OBS_MUSCLE_FORCE: P.nobs += D.nu; break;
       default: delete e; return myo_fail(MYO_ERR_ARG, "unknown obs key");
     }
   }
@@ -263,6 +387,14 @@ int myo_env_create(myo_batch* b, const myo_env_desc* d, myo_env** out) {
     P.T.ctrl_hi = toDevice(d->ctrl_hi, D.nu, e->owned);
     P.T.tau_act = toDevice(d->tau_act, D.nu, e->owned);
     P.T.tau_deact = toDevice(d->tau_deact, D.nu, e->owned);
+    if (d->kind == MYO_ENV_WALK) {
+      P.T.body_mass = toDevice(d->body_mass, D.nbody, e->owned);
+      P.T.alt_qpos = toDevice(d->alt_qpos, D.nq, e->owned);
+      P.T.alt_qvel = toDevice(d->alt_qvel, D.nv, e->owned);
+      void* m = nullptr;
+      if (cudaMalloc(&m, (size_t)b->nworld * sizeof(int)) != cudaSuccess || cudaMemset(m, 0, (size_t)b->nworld * sizeof(int)) != cudaSuccess) throw std::string("cudaMalloc failed");
+      e->owned.push_back(m); P.reset_mask = (int*)m;
+    }
   } catch (const std::string& msg) { myo_env_destroy(e); return myo_fail(MYO_ERR_CUDA, msg); }
   *out = e;
   return MYO_OK;
@@ -298,8 +430,17 @@ static int envReady(myo_env* e) {
   P.qpos = (float*)F.p[MYO_F_QPOS]; P.qvel = (float*)F.p[MYO_F_QVEL]; P.act = (float*)F.p[MYO_F_ACT]; P.ctrl = (float*)F.p[MYO_F_CTRL];
   P.time = (float*)F.p[MYO_F_TIME]; P.warm = (float*)F.p[MYO_F_QACC_WARMSTART]; P.status = (int*)F.p[MYO_F_STATUS];
   if (!P.qpos || !P.qvel || !P.time || !P.warm || (P.na && !P.act) || (P.nu && !P.ctrl)) return myo_fail(MYO_ERR_UNBOUND, "a state field has no bound device buffer");
+  if (P.kind == MYO_ENV_WALK) {
+    P.xpos = (const float*)F.p[MYO_F_XPOS]; P.xquat = (const float*)F.p[MYO_F_XQUAT]; P.xipos = (const float*)F.p[MYO_F_XIPOS]; P.cvel = (const float*)F.p[MYO_F_CVEL];
+    P.actlen = (const float*)F.p[MYO_F_ACTUATOR_LENGTH]; P.actvel = (const float*)F.p[MYO_F_ACTUATOR_VELOCITY]; P.actfrc = (const float*)F.p[MYO_F_ACTUATOR_FORCE];
+    if (!P.xpos || !P.xquat || !P.xipos || !P.cvel || !P.actlen || !P.actvel || !P.actfrc)
+      return myo_fail(MYO_ERR_UNBOUND, "the walk env reads xpos, xquat, xipos, cvel, actuator_length, actuator_velocity and actuator_force: bind them on the batch");
+  }
   if (cudaSetDevice(e->b->model->device) != cudaSuccess) return myo_fail(MYO_ERR_CUDA, "cudaSetDevice failed: libmyostep has no CPU fallback");
   return MYO_OK;
+}
+static int envLaunched() {
+  return cudaPeekAtLastError() == cudaSuccess ? MYO_OK : myo_fail(MYO_ERR_CUDA, std::string("kernel launch failed: ") + cudaGetErrorString(cudaGetLastError()));
 }
 int myo_env_reset(myo_env* e, const int32_t* world_mask_dev, void* stream) {
   int rc = envReady(e);
@@ -307,7 +448,13 @@ int myo_env_reset(myo_env* e, const int32_t* world_mask_dev, void* stream) {
   const EnvParams& P = e->P;
   envResetKernel<<<(P.nworld + 127) / 128, 128, 0, (cudaStream_t)stream>>>(P, world_mask_dev);
   myo_count_launch(1);
-  return cudaPeekAtLastError() == cudaSuccess ? MYO_OK : myo_fail(MYO_ERR_CUDA, std::string("kernel launch failed: ") + cudaGetErrorString(cudaGetLastError()));
+  if (P.kind == MYO_ENV_WALK) {   // robot.reset ends with sim.forward() (robot.py:976-979); the observation reads its outputs
+    rc = myo_forward_masked(e->b, world_mask_dev, stream);
+    if (rc) return rc;
+    envObsKernel<<<(P.nworld + 127) / 128, 128, 0, (cudaStream_t)stream>>>(P);
+    myo_count_launch(1);
+  }
+  return envLaunched();
 }
 int myo_env_step(myo_env* e, void* stream) {
   int rc = envReady(e);
@@ -320,16 +467,37 @@ int myo_env_step(myo_env* e, void* stream) {
   }
   rc = myo_step(e->b, P.frame_skip, stream);
   if (rc) return rc;
+  if (P.kind == MYO_ENV_WALK) {
+    // classic-path observation semantics: position / velocity fields of the stepped state (dm_control Physics.step ends
+    // with mj_step1), then reward / done / reset, a full mj_forward of the worlds that were reset, then the observation
+    rc = myo_forward_posvel(e->b, nullptr, stream);
+    if (rc) return rc;
+    envWalkRewardKernel<<<(P.nworld + 127) / 128, 128, 0, (cudaStream_t)stream>>>(P, 1);
+    myo_count_launch(1);
+    if (P.auto_reset) {
+      rc = myo_forward_masked(e->b, P.reset_mask, stream);
+      if (rc) return rc;
+    }
+    envObsKernel<<<(P.nworld + 127) / 128, 128, 0, (cudaStream_t)stream>>>(P);
+    myo_count_launch(1);
+    return envLaunched();
+  }
   envPostKernel<<<(P.nworld + 127) / 128, 128, 0, (cudaStream_t)stream>>>(P, 1);
   myo_count_launch(1);
-  return cudaPeekAtLastError() == cudaSuccess ? MYO_OK : myo_fail(MYO_ERR_CUDA, std::string("kernel launch failed: ") + cudaGetErrorString(cudaGetLastError()));
+  return envLaunched();
 }
 int myo_env_forward(myo_env* e, void* stream) {
   int rc = envReady(e);
   if (rc) return rc;
+  if (e->P.kind == MYO_ENV_WALK) {   // reads the derived fields as they are: call myo_forward / myo_forward_posvel first if the state was edited
+    envWalkRewardKernel<<<(e->P.nworld + 127) / 128, 128, 0, (cudaStream_t)stream>>>(e->P, 0);
+    envObsKernel<<<(e->P.nworld + 127) / 128, 128, 0, (cudaStream_t)stream>>>(e->P);
+    myo_count_launch(2);
+    return envLaunched();
+  }
   envPostKernel<<<(e->P.nworld + 127) / 128, 128, 0, (cudaStream_t)stream>>>(e->P, 0);
   myo_count_launch(1);
-  return cudaPeekAtLastError() == cudaSuccess ? MYO_OK : myo_fail(MYO_ERR_CUDA, std::string("kernel launch failed: ") + cudaGetErrorString(cudaGetLastError()));
+  return envLaunched();
 }
 
 }  // extern "C"

@@ -59,7 +59,7 @@ void myo_count_launch(int n);
 extern const int kWideOutFields[];
 extern const int kNumWideOutFields;
 int myo_out_upload(int slot, const DevModel& D, const SmemLayout& L, const FieldPtrs& F, void* stream);
-int myo_out_launch(int slot, int nworld, int stride, const int* reset_mask, int do_reset, const float* scratch, void* stream);
+int myo_out_launch(int slot, int nworld, int stride, const int* mask, int posvel, const float* scratch, void* stream);
 int myo_launch_quat_kat(int n, const float* qa, const float* qb, float* prod, float* mat, float* rotated, void* stream);
 
 #endif

@@ -62,12 +62,12 @@ template <int STRIDE> __device__ __forceinline__ void framePose(const CtxT<STRID
 #define OUT_MINBLOCKS 12
 #endif
 template <int STRIDE>
-__global__ void __launch_bounds__(OUT_THREADS, OUT_MINBLOCKS) outKernel(int slot, int nworld, const int* __restrict__ mask, int do_reset,
+__global__ void __launch_bounds__(OUT_THREADS, OUT_MINBLOCKS) outKernel(int slot, int nworld, const int* __restrict__ mask, int posvel,
                                                  const float* __restrict__ scratch) {
   const DevModel& D = oP[slot].D; const SmemLayout& L = oP[slot].L; const FieldPtrs& F = oP[slot].F;
   CtxT<STRIDE> c; c.w = (size_t)blockIdx.x * OUT_THREADS + threadIdx.x; c.nw = (size_t)nworld;
   if (c.w >= c.nw) return;
-  if (do_reset && mask && !mask[c.w]) return;
+  if (mask && !mask[c.w]) return;   // a mask restricts the launch to the flagged worlds
   c.sm = scratch + (c.w / STRIDE) * (size_t)L.total * STRIDE + (c.w % STRIDE);
   const int nv = D.nv;
   void* sp = F.p[MYO_F_SITE_XPOS]; void* smt = F.p[MYO_F_SITE_XMAT]; void* gp = F.p[MYO_F_GEOM_XPOS]; void* gm = F.p[MYO_F_GEOM_XMAT];
@@ -91,6 +91,7 @@ __global__ void __launch_bounds__(OUT_THREADS, OUT_MINBLOCKS) outKernel(int slot
   const int nefc = __float_as_int(S(c, L.counts + 1));   // left by the step kernel: ncon, nefc, niter
   const size_t nw = c.nw, w = c.w;
   for (int it = blockIdx.y; it < n10; it += gridDim.y) {
+    if (posvel && it >= n4 && it < n8) continue;   // position / velocity refresh: inertia, contacts and constraint rows are not recomputed
     if (it < n1) {   // site or geom pose
       const bool site = it < n0;
       const int q = site ? it : it - n0;
@@ -278,7 +279,7 @@ int myo_out_upload(int slot, const DevModel& D, const SmemLayout& L, const Field
   for (int i = 0; i < kNumWideOutFields; i++) P.F.p[kWideOutFields[i]] = F.p[kWideOutFields[i]];
   return cudaMemcpyToSymbolAsync(oP, &P, sizeof(OutParams), (size_t)slot * sizeof(OutParams), cudaMemcpyHostToDevice, (cudaStream_t)stream) == cudaSuccess ? 0 : -1;
 }
-int myo_out_launch(int slot, int nworld, int stride, const int* reset_mask, int do_reset, const float* scratch, void* stream) {
+int myo_out_launch(int slot, int nworld, int stride, const int* mask, int posvel, const float* scratch, void* stream) {
   dim3 grid((nworld + OUT_THREADS - 1) / OUT_THREADS, 1);
   // OUT_MINBLOCKS CTAs are resident per SM; many short CTAs (8 waves) let the hardware scheduler even out the item costs
   static const int want_env = getenv("MYO_OUT_BLOCKS") ? atoi(getenv("MYO_OUT_BLOCKS")) : 0;   // developer knob
@@ -288,11 +289,11 @@ int myo_out_launch(int slot, int nworld, int stride, const int* reset_mask, int 
   if (grid.y > 512) grid.y = 512;
   cudaStream_t st = (cudaStream_t)stream;
   switch (stride) {
-    case 32: outKernel<32><<<grid, OUT_THREADS, 0, st>>>(slot, nworld, reset_mask, do_reset, scratch); break;
-    case 16: outKernel<16><<<grid, OUT_THREADS, 0, st>>>(slot, nworld, reset_mask, do_reset, scratch); break;
-    case 8: outKernel<8><<<grid, OUT_THREADS, 0, st>>>(slot, nworld, reset_mask, do_reset, scratch); break;
-    case 4: outKernel<4><<<grid, OUT_THREADS, 0, st>>>(slot, nworld, reset_mask, do_reset, scratch); break;
-    case 2: outKernel<2><<<grid, OUT_THREADS, 0, st>>>(slot, nworld, reset_mask, do_reset, scratch); break;
+    case 32: outKernel<32><<<grid, OUT_THREADS, 0, st>>>(slot, nworld, mask, posvel, scratch); break;
+    case 16: outKernel<16><<<grid, OUT_THREADS, 0, st>>>(slot, nworld, mask, posvel, scratch); break;
+    case 8: outKernel<8><<<grid, OUT_THREADS, 0, st>>>(slot, nworld, mask, posvel, scratch); break;
+    case 4: outKernel<4><<<grid, OUT_THREADS, 0, st>>>(slot, nworld, mask, posvel, scratch); break;
+    case 2: outKernel<2><<<grid, OUT_THREADS, 0, st>>>(slot, nworld, mask, posvel, scratch); break;
     default: return -1;
   }
   return cudaPeekAtLastError() == cudaSuccess ? 0 : -1;

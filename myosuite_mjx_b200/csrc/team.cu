@@ -1823,7 +1823,10 @@ __device__ __noinline__ void resetState(int slot, SP sm, Tm t) {
 #define PHASE_SYNC() __syncthreads()
 #endif
 // mj_forward for one world: everything from the state in the scratch
-__device__ __forceinline__ void forwardWorld(int slot, int fslot, SP sm, Tm t, World W, bool live, bool last, int* status, int* ncon_o, int* nefc_o, int* niter_o) {
+// posvel: mj_step1-style refresh -- only the position- and velocity-dependent stages run (kinematics, com, tendons,
+// transmission lengths / velocities, body velocities, bias and passive forces); contacts, constraint rows, actuator
+// forces, accelerations and the warm start keep the values of the last full pass.
+__device__ __forceinline__ void forwardWorld(int slot, int fslot, SP sm, Tm t, World W, bool live, bool last, bool posvel, int* status, int* ncon_o, int* nefc_o, int* niter_o) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
   const int nv = D.nv;
   if (live) { kinematics(slot, sm, t); comPos(slot, sm, t); }
@@ -1832,13 +1835,31 @@ __device__ __forceinline__ void forwardWorld(int slot, int fslot, SP sm, Tm t, W
   PHASE_SYNC();
   if (live) tendons(slot, fslot, sm, t, W);
   PHASE_SYNC();
-  if (live) inertia(slot, fslot, sm, t, W);
+  if (live && !posvel) inertia(slot, fslot, sm, t, W);
   PHASE_SYNC();
   int ncon = 0, nefc = 0, niter = 0;
-  if (live && !(D.disableflags & (DSBL_CONTACT | DSBL_CONSTRAINT))) ncon = collision(slot, sm, t, status);
+  if (live && !posvel && !(D.disableflags & (DSBL_CONTACT | DSBL_CONSTRAINT))) ncon = collision(slot, sm, t, status);
   PHASE_SYNC();
   if (live) velocity(slot, fslot, sm, t, W);
   PHASE_SYNC();
+  if (posvel) {   // CTA-uniform
+    if (live) {   // mj_transmission outputs of the refreshed tendon stage (actuation() writes them on a full pass)
+      const FieldPtrs& F = tP[fslot].F;
+      void* olen = F.p[MYO_F_ACTUATOR_LENGTH]; void* ovel = F.p[MYO_F_ACTUATOR_VELOCITY];
+      TFOR(i, D.nu) {
+        const int id = D.act_trnid[i];
+        const float gear = D.act_gear[i];
+        float len, vel;
+        if (D.act_trntype[i] == 3) { len = gear * sm[L.tenlen + id]; vel = gear * sm[L.tenvel + id]; }
+        else { len = gear * sm[L.qpos + D.jnt_qposadr[id]]; vel = gear * sm[L.qvel + D.jnt_dofadr[id]]; }
+        sm[L.actlen + i] = len; sm[L.actvel + i] = vel;
+        if (olen) OUTF(olen, i) = len;
+        if (ovel) OUTF(ovel, i) = vel;
+      }
+    }
+    *ncon_o = 0; *nefc_o = 0; *niter_o = 0;
+    return;
+  }
   if (live) actuation(slot, fslot, sm, t, W);
   PHASE_SYNC();
   if (live) nefc = makeConstraint(slot, sm, t, ncon, status);
@@ -1877,7 +1898,7 @@ __global__ void __launch_bounds__(32 * CTA_WARPS, CTA_MINBLOCKS) stepKernel(int 
   const size_t warp = (size_t)blockIdx.x * CTA_WARPS + (threadIdx.x >> 5);
   Tm t; t.tl = lane % TEAM; t.mask = TEAM == 32 ? 0xffffffffu : (((1u << TEAM) - 1u) << (g * TEAM));
   World W; W.w = warp * SCR_STRIDE + g; W.nw = (size_t)nworld;
-  const bool live = W.w < W.nw && !(do_reset && mask && !mask[W.w]);
+  const bool live = W.w < W.nw && !(mask && !mask[W.w]);   // a mask restricts any launch to the flagged worlds
   if (!live) W.w = 0;
   SP sm; sm.p = scratch + warp * L.total * SCR_STRIDE + g;
   const int nq = D.nq, nv = D.nv, na = D.na, nu = D.nu;
@@ -1900,6 +1921,7 @@ __global__ void __launch_bounds__(32 * CTA_WARPS, CTA_MINBLOCKS) stepKernel(int 
     }
     TSYNC();
   }
+  const bool posvel = forward_only == 2;
   const int nloop = forward_only ? 1 : nsub;
   for (int sub = 0; sub < nloop; sub++) {
     const bool last = sub == nloop - 1;
@@ -1909,7 +1931,7 @@ __global__ void __launch_bounds__(32 * CTA_WARPS, CTA_MINBLOCKS) stepKernel(int 
       if (anyBad(sm + L.qvel, nv, t)) { TSYNC(); resetState(slot, sm, t); status |= MYO_WORLD_BADQVEL; }
     }
     int ncon = 0, nefc = 0, niter = 0;
-    forwardWorld(slot, fslot, sm, t, W, live, last, &status, &ncon, &nefc, &niter);
+    forwardWorld(slot, fslot, sm, t, W, live, last, posvel, &status, &ncon, &nefc, &niter);
     // mj_checkAcc: a world whose qacc went bad is reset (qpos0, zero velocity / activation) and flagged; this substep
     // does not integrate it, its next forward pass starts from the reset state.
     bool skip = false;
@@ -1919,7 +1941,7 @@ __global__ void __launch_bounds__(32 * CTA_WARPS, CTA_MINBLOCKS) stepKernel(int 
       status |= MYO_WORLD_BADQACC;
       skip = true;
     }
-    if (live && last) {
+    if (live && last && !posvel) {
       writeConstraintOutputs(slot, fslot, sm, t, W, ncon, nefc, niter);
       void* o;
       if ((o = F.p[MYO_F_QACC])) TFOR(i, nv) OUTF(o, i) = sm[L.qacc + i];
@@ -1980,7 +2002,7 @@ __global__ void __launch_bounds__(32 * CTA_WARPS, CTA_MINBLOCKS) stepKernel(int 
     TFOR(i, na) OUTF(ga, i) = sm[L.act + i];
     if (t.tl == 0) OUTF(gt, 0) = time;
   }
-  TFOR(i, nv) OUTF(gw, i) = sm[L.warm + i];
+  if (!posvel) TFOR(i, nv) OUTF(gw, i) = sm[L.warm + i];
   if (gs && t.tl == 0) OUTI(gs, 0) = status;
 }
 

@@ -13,10 +13,15 @@ import torch
 from . import lib as _lib
 
 COND = {"": 0, None: 0, "none": 0, "sarcopenia": 1, "fatigue": 2, "reafferentation": 3}
-OBS_KEY = {"time": 0, "qpos": 1, "qvel": 2, "act": 3, "pose_err": 4}
+OBS_KEY = {"time": 0, "qpos": 1, "qvel": 2, "act": 3, "pose_err": 4, "qpos_without_xy": 5, "com_vel": 6, "torso_angle": 7,
+           "feet_heights": 8, "height": 9, "feet_rel_positions": 10, "phase_var": 11, "muscle_length": 12, "muscle_velocity": 13,
+           "muscle_force": 14}
+MAX_OBS_KEYS = 16
 E_FIELDS = ("action", "obs", "reward", "done", "rwd_terms", "target", "fatigue", "steps", "episode")
 E_INT = ("steps", "episode")
-RWD_TERMS = ("pose", "bonus", "penalty", "act_reg", "sparse", "solved")
+RWD_TERMS = ("pose", "bonus", "penalty", "act_reg", "sparse", "solved", "done")
+WALK_RWD_TERMS = ("vel_reward", "cyclic_hip", "ref_rot", "joint_angle_rew", "act_mag", "sparse", "solved", "done")
+WALK_FIELDS = ("xpos", "xquat", "xipos", "cvel", "actuator_length", "actuator_velocity", "actuator_force")   # what the walk obs reads
 
 _i32p, _f32p = ctypes.POINTER(ctypes.c_int32), ctypes.POINTER(ctypes.c_float)
 
@@ -24,7 +29,7 @@ _i32p, _f32p = ctypes.POINTER(ctypes.c_int32), ctypes.POINTER(ctypes.c_float)
 class EnvDesc(ctypes.Structure):
     """struct myo_env_desc"""
     _fields_ = [("frame_skip", ctypes.c_int32), ("normalize_act", ctypes.c_int32), ("muscle_condition", ctypes.c_int32),
-                ("epl_id", ctypes.c_int32), ("eip_id", ctypes.c_int32), ("nobs_keys", ctypes.c_int32), ("obs_keys", ctypes.c_int32 * 8),
+                ("epl_id", ctypes.c_int32), ("eip_id", ctypes.c_int32), ("nobs_keys", ctypes.c_int32), ("obs_keys", ctypes.c_int32 * MAX_OBS_KEYS),
                 ("ntarget", ctypes.c_int32), ("target_type", ctypes.c_int32), ("reset_type", ctypes.c_int32), ("auto_reset", ctypes.c_int32),
                 ("horizon", ctypes.c_int32), ("world_offset", ctypes.c_int32), ("seed", ctypes.c_uint64),
                 ("pose_thd", ctypes.c_float), ("far_th", ctypes.c_float), ("w_pose", ctypes.c_float), ("w_bonus", ctypes.c_float),
@@ -32,7 +37,13 @@ class EnvDesc(ctypes.Structure):
                 ("fatigue_r", ctypes.c_float),
                 ("target_qposadr", _i32p), ("target_range", _f32p), ("target_value", _f32p), ("init_qpos", _f32p), ("init_qvel", _f32p),
                 ("reset_lo", _f32p), ("reset_hi", _f32p), ("act_is_muscle", _i32p), ("ctrl_lo", _f32p), ("ctrl_hi", _f32p),
-                ("tau_act", _f32p), ("tau_deact", _f32p)]
+                ("tau_act", _f32p), ("tau_deact", _f32p),
+                ("kind", ctypes.c_int32), ("foot_l_bid", ctypes.c_int32), ("foot_r_bid", ctypes.c_int32), ("pelvis_bid", ctypes.c_int32),
+                ("torso_bid", ctypes.c_int32), ("hip_flex_adr", ctypes.c_int32 * 2), ("hip_angle_adr", ctypes.c_int32 * 4),
+                ("min_height", ctypes.c_float), ("max_rot", ctypes.c_float), ("hip_period", ctypes.c_float), ("target_x_vel", ctypes.c_float),
+                ("target_y_vel", ctypes.c_float), ("target_rot", ctypes.c_float * 4), ("reset_noise", ctypes.c_float),
+                ("w_vel", ctypes.c_float), ("w_done", ctypes.c_float), ("w_cyclic", ctypes.c_float), ("w_ref_rot", ctypes.c_float),
+                ("w_joint_angle", ctypes.c_float), ("body_mass", _f32p), ("alt_qpos", _f32p), ("alt_qvel", _f32p)]
 
 
 def _bind_protos(L):
@@ -104,6 +115,38 @@ def pose_config(mj, frame_skip=10, normalize_act=True, muscle_condition="", targ
                 fatigue_F=0.00912, fatigue_R=0.1 * 0.00094, fatigue_r=10.0 * 15, na=na, dt=float(mj.opt_timestep) * int(frame_skip))
 
 
+def walk_config(mj, frame_skip=10, normalize_act=True, muscle_condition="", min_height=0.8, max_rot=0.8, hip_period=100, reset_type="init",
+                target_x_vel=0.0, target_y_vel=1.2, target_rot=None, obs_keys=None, weights=None, horizon=1000, auto_reset=True, seed=0,
+                world_offset=0, epl_id=-1, eip_id=-1):
+    """WalkEnvV0 configuration (walk_v0.py:186-257; registered kwargs myobase/__init__.py:445-459).  Start states follow
+    walk_v0.py:340-350: "init" -> keyframe 2, "random" -> keyframe 2 or 3 plus noise, anything else -> keyframe 0."""
+    names_b, names_j = list(mj.names_body), list(mj.names_jnt)
+    qadr = lambda n: int(mj.jnt_qposadr[names_j.index(n)])
+    if obs_keys is None:
+        obs_keys = ["qpos_without_xy", "qvel", "com_vel", "torso_angle", "feet_heights", "height", "feet_rel_positions", "phase_var",
+                    "muscle_length", "muscle_velocity", "muscle_force"]          # walk_v0.py:186-198
+    obs_keys = list(obs_keys)
+    if int(mj.na) > 0 and "act" not in obs_keys:
+        obs_keys.append("act")
+    w = dict(vel_reward=5.0, done=-100.0, cyclic_hip=-10.0, ref_rot=10.0, joint_angle_rew=5.0)    # walk_v0.py:200-206
+    w.update(weights or {})
+    kq, kv = np.asarray(mj.key_qpos, dtype=np.float32), np.asarray(mj.key_qvel, dtype=np.float32)
+    k0 = 2 if reset_type in ("init", "random") else 0
+    base = pose_config(mj, frame_skip=frame_skip, normalize_act=normalize_act, muscle_condition=muscle_condition, obs_keys=("qpos",),
+                       horizon=horizon, auto_reset=auto_reset, seed=seed, world_offset=world_offset, epl_id=epl_id, eip_id=eip_id,
+                       target_jnt_value=np.zeros(int(mj.nq)), init_qpos=kq[k0], init_qvel=kv[k0])
+    base.update(kind="walk", obs_keys=obs_keys, reset_type=reset_type, target_qposadr=np.zeros(0, np.int32), target_value=None, target_range=None,
+                foot_l=names_b.index("talus_l"), foot_r=names_b.index("talus_r"), pelvis=names_b.index("pelvis"), torso=names_b.index("torso"),
+                hip_flex=[qadr("hip_flexion_l"), qadr("hip_flexion_r")],
+                hip_angle=[qadr(n) for n in ("hip_adduction_l", "hip_adduction_r", "hip_rotation_l", "hip_rotation_r")],
+                min_height=float(min_height), max_rot=float(max_rot), hip_period=float(hip_period), target_x_vel=float(target_x_vel),
+                target_y_vel=float(target_y_vel),
+                target_rot=np.asarray(target_rot if target_rot is not None else kq[0][3:7], dtype=np.float32),   # init_qpos = key 0 (walk_v0.py:253)
+                reset_noise=0.02, walk_weights=(w["vel_reward"], w["done"], w["cyclic_hip"], w["ref_rot"], w["joint_angle_rew"]),
+                body_mass=np.asarray(mj.body_mass, dtype=np.float32), alt_qpos=kq[3], alt_qvel=kv[3])
+    return base
+
+
 class FusedEnv:
     """myo_env handle bound to a `mjx.Data` batch; env buffers are torch tensors in the [k, nworld] layout."""
 
@@ -139,6 +182,18 @@ class FusedEnv:
         d.act_is_muscle = arr(cfg["act_is_muscle"], np.int32)
         d.ctrl_lo, d.ctrl_hi = arr(cfg["ctrl_lo"], np.float32), arr(cfg["ctrl_hi"], np.float32)
         d.tau_act, d.tau_deact = arr(cfg["tau_act"], np.float32), arr(cfg["tau_deact"], np.float32)
+        if cfg.get("kind") == "walk":
+            d.kind = 1
+            d.foot_l_bid, d.foot_r_bid, d.pelvis_bid, d.torso_bid = cfg["foot_l"], cfg["foot_r"], cfg["pelvis"], cfg["torso"]
+            for i in range(2):
+                d.hip_flex_adr[i] = cfg["hip_flex"][i]
+            for i in range(4):
+                d.hip_angle_adr[i] = cfg["hip_angle"][i]
+                d.target_rot[i] = float(cfg["target_rot"][i])
+            d.min_height, d.max_rot, d.hip_period = cfg["min_height"], cfg["max_rot"], cfg["hip_period"]
+            d.target_x_vel, d.target_y_vel, d.reset_noise = cfg["target_x_vel"], cfg["target_y_vel"], cfg["reset_noise"]
+            d.w_vel, d.w_done, d.w_cyclic, d.w_ref_rot, d.w_joint_angle = cfg["walk_weights"]
+            d.body_mass, d.alt_qpos, d.alt_qvel = arr(cfg["body_mass"], np.float32), arr(cfg["alt_qpos"], np.float32), arr(cfg["alt_qvel"], np.float32)
         h = ctypes.c_void_p()
         _lib.check(L.myo_env_create(data._h, ctypes.byref(d), ctypes.byref(h)))
         self._h = h

@@ -188,9 +188,27 @@ def put_data(model, mj_data=None, nworld=1, fields="all", nconmax=0, njmax=0) ->
     return d
 
 
-def forward(model, data) -> Data:
-    """mjx.forward / mj_forward (reference: sim.forward(), myosuite/robot/robot.py:979)."""
-    _lib.check(_lib.lib().myo_forward(data._h, _stream()))
+def _mask_ptr(data, mask):
+    if mask is None:
+        return None, None
+    mask = mask.to(device=data.qpos.device, dtype=torch.int32).reshape(-1).contiguous()
+    return ctypes.c_void_p(mask.data_ptr()), mask
+
+
+def forward(model, data, mask=None) -> Data:
+    """mjx.forward / mj_forward (reference: sim.forward(), myosuite/robot/robot.py:979); `mask` restricts it to the
+    flagged worlds."""
+    p, keep = _mask_ptr(data, mask)
+    _lib.check(_lib.lib().myo_forward_masked(data._h, p, _stream()) if mask is not None else _lib.lib().myo_forward(data._h, _stream()))
+    return data
+
+
+def refresh(model, data, mask=None) -> Data:
+    """mj_step1-style refresh of the position- and velocity-dependent fields from the current state (what dm_control's
+    Physics.step leaves behind on the classic path, reference: myosuite/physics/mj_sim_scene.py:55); contacts, forces,
+    accelerations and the warm start are left as the last full pass wrote them."""
+    p, keep = _mask_ptr(data, mask)
+    _lib.check(_lib.lib().myo_forward_posvel(data._h, p, _stream()))
     return data
 
 

@@ -125,3 +125,34 @@ class PoseEnv(PipelineEnv):
         self.env.step(action)
         state.metrics.update(**self._metrics())
         return state.replace(pipeline_state=self._data, obs=self.env.obs, reward=self.env.reward[:, 0], done=self.env.done[:, 0])
+
+
+class WalkEnv(PipelineEnv):
+    """myoLegWalk (reference: myosuite/envs/myo/myobase/walk_v0.py WalkEnvV0) in the reset(rng) / step(State, action)
+    shape.  The observation reads position- and velocity-dependent mjData fields of the stepped state, as the classic
+    path does (dm_control's Physics.step ends with mj_step1): see myo_forward_posvel in include/myostep.h."""
+
+    def __init__(self, sys, n_frames=10, nworld=1, fields=None, **kw):
+        from . import envs
+        base_kw = {k: kw.pop(k) for k in ("device", "nconmax", "njmax", "backend") if k in kw}
+        if fields is None:
+            fields = mjx.CORE_FIELDS + envs.WALK_FIELDS
+        super().__init__(sys, n_frames=n_frames, nworld=nworld, fields=fields, **base_kw)
+        self.cfg = envs.walk_config(self.sys.mj, frame_skip=n_frames, **kw)
+        self.env = envs.FusedEnv(self._data, self.cfg)
+
+    def _metrics(self):
+        terms = self.env.rwd_terms
+        from .envs import WALK_RWD_TERMS
+        return {k: terms[:, i] for i, k in enumerate(WALK_RWD_TERMS)}
+
+    def reset(self, rng) -> State:
+        self.env.seed(int(rng))
+        self.env.storage("episode").zero_()
+        self.env.reset()
+        return State(self._data, self.env.obs, self.env.reward[:, 0], self.env.done[:, 0], self._metrics())
+
+    def step(self, state: State, action) -> State:
+        self.env.step(action)
+        state.metrics.update(**self._metrics())
+        return state.replace(pipeline_state=self._data, obs=self.env.obs, reward=self.env.reward[:, 0], done=self.env.done[:, 0])

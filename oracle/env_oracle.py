@@ -157,3 +157,40 @@ class PoseEnvOracle:
             for w in np.nonzero(ended)[0]:
                 self._reset_world(w)
         return self._obs()[1], r, ended
+
+
+# ---------------------------------------------------------------------------------------------------- walk env
+def quat2mat00(q):
+    """[0, 0] entry of myosuite/utils/quat_math.py:160-183 quat2mat."""
+    q = np.asarray(q, float)
+    Nq = np.sum(q * q, axis=-1)
+    s = 2.0 / Nq
+    return np.where(Nq > np.finfo(np.float64).eps, 1.0 - (q[..., 2] * (q[..., 2] * s) + q[..., 3] * (q[..., 3] * s)), 1.0)
+
+
+def walk_obs_reward(c, qpos, qvel, act, cvel, xipos, xpos, xquat, alen, avel, afrc, steps):
+    """walk_v0.py:263-310 with the helpers :352-478, batched over the leading axis.  `c`: envs.walk_config dict; `steps`
+    is the reference's self.steps at evaluation time.  Returns (obs_dict, reward_dict)."""
+    mass = np.asarray(c["body_mass"], float)[:, None]
+    com_vel = (np.sum(mass * -np.asarray(cvel, float), axis=-2) / np.sum(mass))[..., 3:5]
+    height = (np.sum(mass * np.asarray(xipos, float), axis=-2) / np.sum(mass))[..., 2]
+    phase = (np.asarray(steps) / c["hip_period"]) % 1
+    fl, fr, pe, to = c["foot_l"], c["foot_r"], c["pelvis"], c["torso"]
+    od = {"qpos_without_xy": qpos[..., 2:], "qvel": qvel * c["dt"], "com_vel": com_vel, "torso_angle": xquat[..., to, :],
+          "feet_heights": np.stack([xpos[..., fl, 2], xpos[..., fr, 2]], axis=-1), "height": height[..., None],
+          "feet_rel_positions": np.concatenate([xpos[..., fl, :] - xpos[..., pe, :], xpos[..., fr, :] - xpos[..., pe, :]], axis=-1),
+          "phase_var": phase[..., None], "muscle_length": alen, "muscle_velocity": np.clip(avel, -100, 100),
+          "muscle_force": np.clip(afrc / 1000, -100, 100), "act": act}
+    vel_reward = np.exp(-np.square(c["target_y_vel"] - com_vel[..., 1])) + np.exp(-np.square(c["target_x_vel"] - com_vel[..., 0]))
+    des = np.stack([0.8 * np.cos(phase * 2 * np.pi + np.pi), 0.8 * np.cos(phase * 2 * np.pi)], axis=-1).astype(np.float32)
+    cyclic = np.linalg.norm(des - qpos[..., c["hip_flex"]], axis=-1)
+    ref_rot = np.exp(-np.linalg.norm(5.0 * (qpos[..., 3:7] - np.asarray(c["target_rot"], float)), axis=-1))
+    joint_angle = np.exp(-5 * np.mean(np.abs(qpos[..., c["hip_angle"]]), axis=-1))
+    na = act.shape[-1]
+    act_mag = np.linalg.norm(act, axis=-1) / na if na else 0
+    done = (height < c["min_height"]) | (np.abs(quat2mat00(qpos[..., 3:7])) > c["max_rot"])
+    w = c["walk_weights"]
+    r = {"vel_reward": vel_reward, "cyclic_hip": cyclic, "ref_rot": ref_rot, "joint_angle_rew": joint_angle, "act_mag": act_mag,
+         "sparse": vel_reward, "solved": vel_reward >= 1.0, "done": done}
+    r["dense"] = w[0] * vel_reward + w[1] * done + w[2] * cyclic + w[3] * ref_rot + w[4] * joint_angle
+    return od, r

@@ -40,7 +40,7 @@ def test_pose_env_reset_step_shapes(models):
     st = env.reset(1234)
     # obs = qpos, qvel * dt, pose_err, act (pose_v0.py:15 + base_v0.py:34-38)
     assert st.obs.shape == (64, 2 * m.nq + m.nv + m.na) and st.reward.shape == (64,) and st.done.shape == (64,)
-    assert set(st.metrics) == {"pose", "bonus", "penalty", "act_reg", "sparse", "solved"}
+    assert set(st.metrics) == {"pose", "bonus", "penalty", "act_reg", "sparse", "solved", "done"}
     lo = torch.as_tensor(np.asarray(m.jnt_range)[:, 0], device="cuda", dtype=torch.float32)
     hi = torch.as_tensor(np.asarray(m.jnt_range)[:, 1], device="cuda", dtype=torch.float32)
     assert bool(((st.pipeline_state.qpos >= lo - 1e-6) & (st.pipeline_state.qpos <= hi + 1e-6)).all())
@@ -125,7 +125,7 @@ def test_env_forward_matches_reference_golden(models):
     assert safe.sum() > 0.95 * n
     for i, k in enumerate(envs.RWD_TERMS):
         g = GOLD["rwd_" + k].astype(np.float64)
-        sel = safe if k in ("bonus", "penalty", "solved") else slice(None)
+        sel = safe if k in ("bonus", "penalty", "solved", "done") else slice(None)
         assert np.abs(terms[:, i][sel] - g[sel]).max() <= 2e-6 * max(1.0, np.abs(g).max()), k
     assert np.abs(env.reward.cpu().numpy()[:, 0][safe] - GOLD["rwd_dense"][safe]).max() < 1e-4      # weights up to 50
     assert np.array_equal(env.done.cpu().numpy()[:, 0][safe] > 0, GOLD["rwd_done"][safe] > 0)
@@ -200,6 +200,110 @@ def test_env_world_offset_partition(models):
         assert torch.equal(sf.obs[:4], sl.obs) and torch.equal(sf.obs[4:], sh.obs)
         assert torch.equal(sf.reward[4:], sh.reward) and torch.equal(sf.done[:4], sl.done)
     assert int(full.env.episode.min()) == 3
+
+
+def test_walk_forward_matches_reference_golden(models):
+    """Walk obs / reward terms / done of given mjData fields against the reference's own WalkEnvV0.get_obs_dict /
+    get_reward_dict (tests/golden/make_walk_kat.py).  float32 tolerance: obs 2e-6 relative to the largest entry of each key
+    (inputs are float32-exact), reward terms 2e-5 (exp of float32 sums), dense 2e-3 (weights up to 100)."""
+    import torch
+    from myosuite_mjx_b200 import envs, pipeline
+    W = np.load(os.path.join(os.path.dirname(__file__), "golden", "walk_kat.npz"))
+    m = models("legs")
+    n = W["qpos"].shape[0]
+    env = pipeline.WalkEnv(m, nworld=n, auto_reset=False, horizon=0)
+    env.reset(0)
+    d, e = env._data, env.env
+    put = lambda t, a: t.copy_(torch.as_tensor(np.asarray(a, dtype=np.float32).reshape(n, -1), device=t.device).reshape(t.shape))
+    put(d.qpos, W["qpos"]); put(d.qvel, W["qvel"]); put(d.act, W["act"]); put(d.cvel, W["cvel"]); put(d.xipos, W["xipos"]); put(d.xpos, W["xpos"])
+    put(d.xquat, W["xquat"]); put(d.actuator_length, W["actuator_length"]); put(d.actuator_velocity, W["actuator_velocity"])
+    put(d.actuator_force, W["actuator_force"])
+    e.steps.copy_(torch.as_tensor(W["steps"][:, None] + 1, dtype=torch.int32, device="cuda"))     # the reference's self.steps lags by one
+    e.forward()
+    obs = e.obs.cpu().numpy()
+    o = 0
+    for k in env.cfg["obs_keys"]:
+        ref = W["obs_" + k]
+        got = obs[:, o:o + ref.shape[1]]; o += ref.shape[1]
+        assert np.abs(got - ref).max() <= 2e-6 * max(1.0, np.abs(ref).max()), k
+    assert o == obs.shape[1]
+    terms = e.rwd_terms.cpu().numpy()
+    height = W["obs_height"][:, 0]
+    safe = np.abs(height - 0.8) > 1e-5
+    for i, k in enumerate(envs.WALK_RWD_TERMS):
+        g = W["rwd_" + k].astype(np.float64)
+        sel = safe if k in ("done", "solved") else slice(None)
+        assert np.abs(terms[:, i][sel] - g[sel]).max() <= 2e-5 * max(1.0, np.abs(g).max()), k
+    assert np.abs(e.reward.cpu().numpy()[:, 0][safe] - W["rwd_dense"][safe]).max() < 2e-3
+    assert np.array_equal(e.done.cpu().numpy()[:, 0][safe] > 0, W["rwd_done"][safe] > 0)
+
+
+def test_walk_env_step_semantics(models):
+    """myoLegWalk-v0 through the registry: (1) after a step the observation's position / velocity entries describe the
+    STEPPED state (classic-path semantics, dm_control's trailing mj_step1) -- checked against a full mj_forward of a copy
+    of the state; (2) actuator_force keeps the last step's value; (3) worlds that fall are reset to the keyframe and
+    their observation is the keyframe's; (4) the whole observation equals the oracle's walk_obs_reward of the bound fields."""
+    import env_oracle as eo
+    import torch
+    from myosuite_mjx_b200 import mjx, registry
+    m = models("legs")
+    nw = 16
+    env = registry.make("myoLegWalk-v0", nworld=nw, model=m, horizon=12)
+    st = env.reset(5)
+    d, e, c = env._data, env.env, env.cfg
+    obs0 = st.obs.clone()
+    assert obs0.shape == (nw, sum({"qpos_without_xy": 33, "qvel": 34, "com_vel": 2, "torso_angle": 4, "feet_heights": 2, "height": 1,
+                                   "feet_rel_positions": 6, "phase_var": 1, "muscle_length": 80, "muscle_velocity": 80, "muscle_force": 80, "act": 80}[k] for k in c["obs_keys"]))
+    key2 = np.asarray(m.key_qpos, dtype=np.float32)[2]
+    assert np.array_equal(d.qpos.cpu().numpy(), np.tile(key2, (nw, 1)))
+    g = torch.Generator(device="cuda"); g.manual_seed(3)
+    saw_reset = False
+    for t in range(14):
+        a = torch.rand((nw, m.nu), generator=g, device="cuda") * 2 - 1
+        frc_before = None
+        st = env.step(st, a)
+        ended = st.done.cpu().numpy() > 0
+        f = lambda name: getattr(d, name).cpu().numpy().astype(np.float64)
+        steps_ref = np.maximum(e.steps.cpu().numpy()[:, 0] - 1, 0)
+        od, r = eo.walk_obs_reward(c, f("qpos"), f("qvel"), f("act"), f("cvel").reshape(nw, -1, 6), f("xipos").reshape(nw, -1, 3),
+                                   f("xpos").reshape(nw, -1, 3), f("xquat").reshape(nw, -1, 4), f("actuator_length"), f("actuator_velocity"),
+                                   f("actuator_force"), steps_ref)
+        ref = np.concatenate([od[k] for k in c["obs_keys"]], axis=-1)
+        assert np.abs(st.obs.cpu().numpy() - ref).max() < 1e-4 * max(1.0, np.abs(ref).max()), t
+        # (1) refreshed fields == full forward of the same state
+        chk = d.clone()
+        mjx.forward(env.sys, chk)
+        for name in ("xpos", "xipos", "xquat", "cvel", "actuator_length", "actuator_velocity"):
+            a_, b_ = getattr(d, name).cpu().numpy(), getattr(chk, name).cpu().numpy()
+            assert np.abs(a_ - b_).max() <= 1e-5 * max(1.0, np.abs(b_).max()), (t, name)
+        if ended.any():
+            saw_reset = True
+            assert np.array_equal(d.qpos.cpu().numpy()[ended], np.tile(key2, (int(ended.sum()), 1)))
+            assert np.abs(st.obs.cpu().numpy()[ended] - obs0.cpu().numpy()[ended]).max() < 1e-6
+            assert (e.steps.cpu().numpy()[ended, 0] == 0).all()
+        else:
+            # (2) the force entries are the last mj_step's, not the refreshed state's
+            assert np.abs(d.actuator_force.cpu().numpy() - chk.actuator_force.cpu().numpy()).max() > 1e-3
+    assert saw_reset and torch.isfinite(st.obs).all() and torch.isfinite(st.reward).all()
+
+
+def test_registry_pose_envs(models):
+    """The registered kwargs of the BASELINE pose configs (myobase/__init__.py) reach the device env."""
+    import torch
+    from myosuite_mjx_b200 import registry
+    for env_id, fixture, thd in (("myoElbowPose1D6MRandom-v0", "elbow", 0.175), ("myoFingerPoseRandom-v0", "finger", 0.35), ("myoHandPoseRandom-v0", "hand_pose", 0.7)):
+        m = models(fixture)
+        env = registry.make(env_id, nworld=32, model=m)
+        assert env.cfg["pose_thd"] == pytest.approx(thd) and env.cfg["horizon"] == 100 and env.cfg["frame_skip"] == 10
+        st = env.reset(11)
+        tr = torch.as_tensor(env.cfg["target_range"], device="cuda")
+        assert bool(((env.target >= tr[:, 0] - 1e-6) & (env.target <= tr[:, 1] + 1e-6)).all())
+        for _ in range(3):
+            st = env.step(st, torch.zeros((32, m.nu), device="cuda"))
+        assert torch.isfinite(st.obs).all() and st.obs.shape[1] == 2 * m.nq + m.nv + m.na
+    env = registry.make("myoHandPose3Fixed-v0", nworld=4, model=models("hand_pose"))
+    env.reset(0)
+    assert np.allclose(env.target.cpu().numpy(), np.tile(registry.ASL_QPOS[3].astype(np.float32), (4, 1)))
 
 
 def test_full_size_properties(models):

@@ -85,3 +85,23 @@ def test_env_oracle_auto_reset_and_partition():
         assert e_full.all() == ((t + 1) % 3 == 0)
     assert (full.episode == 3).all() and (full.steps == 1).all()
     assert len(np.unique(full.target[:, 0])) == 6
+
+
+def test_walk_obs_and_reward_match_reference(models):
+    """oracle/env_oracle.walk_obs_reward against vectors produced by the reference's own WalkEnvV0.get_obs_dict /
+    get_reward_dict (tests/golden/make_walk_kat.py)."""
+    from myosuite_mjx_b200 import envs
+    W = np.load(os.path.join(os.path.dirname(__file__), "golden", "walk_kat.npz"))
+    c = envs.walk_config(models("legs"))
+    assert [k for k in c["obs_keys"] if k != "act"] == list(W["default_obs_keys"])
+    assert tuple(c["walk_weights"]) == tuple(W["weights"])
+    f = lambda k: W[k].astype(np.float64)
+    od, r = eo.walk_obs_reward(c, f("qpos"), f("qvel"), f("act"), f("cvel"), f("xipos"), f("xpos"), f("xquat"), f("actuator_length"),
+                               f("actuator_velocity"), f("actuator_force"), W["steps"])
+    for k in od:
+        np.testing.assert_allclose(od[k], W["obs_" + k], rtol=1e-6, atol=1e-7, err_msg=k)   # float32 masses / keyframe vs the reference's float64
+    for k in ("vel_reward", "cyclic_hip", "ref_rot", "joint_angle_rew", "act_mag", "sparse", "dense"):
+        np.testing.assert_allclose(r[k], W["rwd_" + k], rtol=2e-6, atol=2e-6, err_msg=k)
+    np.testing.assert_array_equal(r["done"], W["rwd_done"] > 0)
+    np.testing.assert_array_equal(r["solved"], W["rwd_solved"] > 0)
+    assert 0.2 < r["done"].mean() < 0.8
