@@ -142,10 +142,12 @@ __device__ __forceinline__ SPI asInt(SP s) { SPI r; r.p = (int*)s.p; return r; }
 // Dense Newton Hessian (nv x nv) of this lane's world.  It is the most re-read block of the solver (assembly, Cholesky,
 // two triangular solves per iteration), so it lives in shared memory -- same interleaving as the scratch, one
 // [nv*nv][SCR_STRIDE] tile per warp -- whenever the CTA's tiles fit (hshared, set at upload), else in the scratch.
+// Only the lower triangle is stored, row-packed: element (r, c <= r) at TRI(r) + c.
+#define TRI(r) (((r) * ((r) + 1)) >> 1)
 extern __shared__ float ctaShared[];
 __device__ __forceinline__ SP hessian(SP sm, int offH, int nv, int hshared) {
   if (!hshared) return sm + offH;
-  SP r; r.p = ctaShared + (threadIdx.x >> 5) * (nv * nv * SCR_STRIDE) + (threadIdx.x & 31) / TEAM;
+  SP r; r.p = ctaShared + (threadIdx.x >> 5) * (TRI(nv) * SCR_STRIDE) + (threadIdx.x & 31) / TEAM;
   return r;
 }
 
@@ -1464,16 +1466,16 @@ __device__ __noinline__ void hessianFactor(int slot, SP sm, Tm t, int ncon, int 
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
   const int nv = D.nv, nb = D.maxbase;
   auto H = hessian(sm, L.H, nv, L.hshared);
-  TFOR(i, nv * nv) H[i] = 0.f;
+  TFOR(i, TRI(nv)) H[i] = 0.f;
   TSYNC();
-  TFOR(e, D.nM) H[D.M_row[e] * nv + D.M_col[e]] = sm[L.qM + e];
+  TFOR(e, D.nM) H[TRI(D.M_row[e]) + D.M_col[e]] = sm[L.qM + e];
   TSYNC();
   TFOR(k, nv) {
     const int li = D.dof_limidx[k];
     if (li < 0) continue;
     for (int q = 0; q < 2; q++) {
       const int r = __float_as_int(sm[L.limrow + 2 * li + q]);
-      if (r >= 0 && EFC(E_JAR, r) < 0.f) H[k * nv + k] += EFC(E_D, r);
+      if (r >= 0 && EFC(E_JAR, r) < 0.f) H[TRI(k) + k] += EFC(E_D, r);
     }
   }
   TSYNC();
@@ -1481,8 +1483,8 @@ __device__ __noinline__ void hessianFactor(int slot, SP sm, Tm t, int ncon, int 
     for (int e = 0; e < D.neq; e++) {
       const int d1 = D.eq_dof1[e], d2 = D.eq_dof2[e];
       const float Dr = EFC(E_D, e), c = EFC(E_COEF, e);
-      H[d1 * nv + d1] += Dr;
-      if (d2 >= 0) { H[max(d1, d2) * nv + min(d1, d2)] += Dr * c; H[d2 * nv + d2] += Dr * c * c; }
+      H[TRI(d1) + d1] += Dr;
+      if (d2 >= 0) { H[TRI(max(d1, d2)) + min(d1, d2)] += Dr * c; H[TRI(d2) + d2] += Dr * c * c; }
     }
   for (int lt = 0; lt < D.nlimt; lt++)
     for (int q = 0; q < 2; q++) {
@@ -1494,7 +1496,7 @@ __device__ __noinline__ void hessianFactor(int slot, SP sm, Tm t, int ncon, int 
       TFOR(i, cnt * cnt) {
         const int a = i / cnt, b = i - a * cnt;
         const int da = D.nz_dof[n0 + a], db = D.nz_dof[n0 + b];
-        if (da >= db) H[da * nv + db] += Dr * sm[L.tenJ + n0 + a] * sm[L.tenJ + n0 + b];
+        if (da >= db) H[TRI(da) + db] += Dr * sm[L.tenJ + n0 + a] * sm[L.tenJ + n0 + b];
       }
     }
   TSYNC();
@@ -1531,7 +1533,7 @@ __device__ __noinline__ void hessianFactor(int slot, SP sm, Tm t, int ncon, int 
         const float jt = Jn[k * nv + r];
         un = fmaf(Wnt[k - 1], jt, un); ut[k - 1] = fmaf(Wnt[k - 1], jn, Wtt[k - 1] * jt);
       }
-      auto Hr = H + r * nv;
+      auto Hr = H + TRI(r);
       #pragma unroll 1
       for (int half = 0; half < 2; half++) {
         unsigned w;
@@ -1556,33 +1558,34 @@ __device__ __noinline__ void hessianFactor(int slot, SP sm, Tm t, int ncon, int 
   for (int j = 0; j < nv; j++) {
     float sj = 0.f;
     for (int r = j + t.tl; r < nv; r += TEAM) {
-      float s0 = H[r * nv + j], s1 = 0.f;
+      auto Hr = H + TRI(r); auto Hj = H + TRI(j);
+      float s0 = Hr[j], s1 = 0.f;
       int k = 0;
-      for (; k + 1 < j; k += 2) { s0 = fmaf(-H[r * nv + k], H[j * nv + k], s0); s1 = fmaf(-H[r * nv + k + 1], H[j * nv + k + 1], s1); }
-      if (k < j) s0 = fmaf(-H[r * nv + k], H[j * nv + k], s0);
+      for (; k + 1 < j; k += 2) { s0 = fmaf(-Hr[k], Hj[k], s0); s1 = fmaf(-Hr[k + 1], Hj[k + 1], s1); }
+      if (k < j) s0 = fmaf(-Hr[k], Hj[k], s0);
       s0 += s1;
-      if (r == j) sj = s0; else H[r * nv + j] = s0;
+      if (r == j) sj = s0; else Hr[j] = s0;
     }
     sj = teamBcast(t, sj, 0);
     const float d = sqrtf(fmaxf(sj, MINVAL)), inv = 1.f / d;
-    for (int r = j + t.tl; r < nv; r += TEAM) { if (r == j) H[j * nv + j] = d; else H[r * nv + j] *= inv; }
+    for (int r = j + t.tl; r < nv; r += TEAM) { if (r == j) H[TRI(j) + j] = d; else H[TRI(r) + j] *= inv; }
     TSYNC();
   }
 }
 __device__ __noinline__ void cholSolve(int slot, SP H, SP x, Tm t) {
   const int nv = tP[slot].D.nv;
   for (int j = 0; j < nv; j++) {
-    const float xj = x[j] / H[j * nv + j];
+    const float xj = x[j] / H[TRI(j) + j];
     TSYNC();
     if (t.tl == 0) x[j] = xj;
-    for (int r = j + 1 + t.tl; r < nv; r += TEAM) x[r] = fmaf(-H[r * nv + j], xj, x[r]);
+    for (int r = j + 1 + t.tl; r < nv; r += TEAM) x[r] = fmaf(-H[TRI(r) + j], xj, x[r]);
     TSYNC();
   }
   for (int j = nv - 1; j >= 0; j--) {
-    const float xj = x[j] / H[j * nv + j];
+    const float xj = x[j] / H[TRI(j) + j];
     TSYNC();
     if (t.tl == 0) x[j] = xj;
-    for (int r = t.tl; r < j; r += TEAM) x[r] = fmaf(-H[j * nv + r], xj, x[r]);
+    for (int r = t.tl; r < j; r += TEAM) x[r] = fmaf(-H[TRI(j) + r], xj, x[r]);
     TSYNC();
   }
 }
@@ -1889,8 +1892,10 @@ __device__ __forceinline__ void forwardWorld(int slot, int fslot, SP sm, Tm t, W
 #ifndef CTA_MINBLOCKS
 #define CTA_MINBLOCKS 1
 #endif
+#ifndef HSHARED_MAX_BYTES
 #define HSHARED_MAX_BYTES (200 * 1024)
-static inline size_t hessianTileBytes(int nv) { return (size_t)CTA_WARPS * SCR_STRIDE * nv * nv * sizeof(float); }
+#endif
+static inline size_t hessianTileBytes(int nv) { return (size_t)CTA_WARPS * SCR_STRIDE * TRI(nv) * sizeof(float); }
 __global__ void __launch_bounds__(32 * CTA_WARPS, CTA_MINBLOCKS) stepKernel(int slot, int nworld, int nsub, int forward_only, const int* __restrict__ mask,
                                                              int do_reset, float* __restrict__ scratch) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L; const FieldPtrs& F = tP[slot].F;
@@ -2044,6 +2049,16 @@ int VFN(myo_team_launch_)(int slot, const SmemLayout& L, int nworld, int nsub, i
     if (cudaFuncSetAttribute(stepKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)HSHARED_MAX_BYTES) != cudaSuccess) return -1;
     configured[dev] = true;
   }
+#ifdef CARVEOUT_EXACT   // ask for the smallest shared-memory carveout that holds the tiles: the rest of the 256 KB stays L1
+  {
+    static int carved[64] = {0};
+    const int pct = shmem == 0 ? 0 : (int)(((shmem + 1024) * 100 + 228 * 1024 - 1) / (228 * 1024));
+    if (cudaGetDevice(&dev) == cudaSuccess && dev >= 0 && dev < 64 && carved[dev] != pct + 1) {
+      cudaFuncSetAttribute(stepKernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
+      carved[dev] = pct + 1;
+    }
+  }
+#endif
   stepKernel<<<(nwarp + CTA_WARPS - 1) / CTA_WARPS, 32 * CTA_WARPS, shmem, (cudaStream_t)stream>>>(slot, nworld, nsub, forward_only, reset_mask, do_reset, scratch);
   return cudaPeekAtLastError() == cudaSuccess ? 0 : -1;
 }
