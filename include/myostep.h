@@ -72,6 +72,10 @@ typedef struct myo_model_desc {
   /* explicit contact pairs and excludes */
   const int32_t *pair_dim, *pair_geom1, *pair_geom2, *exclude_signature;
   const double *pair_solref, *pair_solimp, *pair_margin, *pair_gap, *pair_friction;
+  /* touch sensors (mjSENS_TOUCH only; myolegs_assets.xml:106-110): the sensor's site, and every site's shape for the zone test */
+  int32_t nsensor;
+  const int32_t *sensor_objid, *site_type;
+  const double *site_size;
 } myo_model_desc;
 
 /* status codes */
@@ -169,6 +173,8 @@ typedef enum myo_field {
   MYO_F_SOLVER_NITER,    /* [1] int32 */
   MYO_F_STATUS,          /* [1] int32, MYO_WORLD_* bits, sticky until myo_reset */
   MYO_F_QFRC_APPLIED,    /* [nv]   optional input (mjData.qfrc_applied): added to qfrc_smooth when bound */
+  MYO_F_SENSORDATA,      /* [nsensor] touch sensors (mj_sensorAcc): summed normal force of the contacts of the site's body whose
+                            normal ray meets the site's volume */
   MYO_F_COUNT
 } myo_field;
 

@@ -42,7 +42,7 @@ const char* kFieldNames[MYO_F_COUNT] = {
     "qfrc_passive", "qfrc_spring", "qfrc_damper", "qfrc_actuator", "qfrc_smooth", "qfrc_constraint", "qfrc_inverse", "ncon",
     "nefc", "contact_geom", "contact_dim", "contact_efc_address", "contact_dist", "contact_pos", "contact_frame",
     "contact_includemargin", "contact_friction", "contact_solref", "contact_solimp", "efc_J", "efc_pos", "efc_margin", "efc_D",
-    "efc_aref", "efc_force", "efc_type", "solver_niter", "status", "qfrc_applied"};
+    "efc_aref", "efc_force", "efc_type", "solver_niter", "status", "qfrc_applied", "sensordata"};
 
 bool isIntField(int f) {
   switch (f) {
@@ -60,6 +60,7 @@ int64_t fieldCount(const DevModel& D, int f) {
     case MYO_F_QFRC_CONSTRAINT: case MYO_F_QFRC_INVERSE: case MYO_F_QFRC_APPLIED: return nv;
     case MYO_F_ACT: case MYO_F_ACT_DOT: return D.na;
     case MYO_F_CTRL: case MYO_F_ACTUATOR_LENGTH: case MYO_F_ACTUATOR_VELOCITY: case MYO_F_ACTUATOR_FORCE: return D.nu;
+    case MYO_F_SENSORDATA: return D.nsensor;
     case MYO_F_TIME: case MYO_F_NCON: case MYO_F_NEFC: case MYO_F_SOLVER_NITER: case MYO_F_STATUS: return 1;
     case MYO_F_XPOS: case MYO_F_XIPOS: case MYO_F_SUBTREE_COM: return 3 * nb;
     case MYO_F_XQUAT: return 4 * nb;

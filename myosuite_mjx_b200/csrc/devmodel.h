@@ -26,6 +26,9 @@ enum { ENT_ALWAYS = 0, ENT_NOWRAP = 1, ENT_WRAP = 2 };
 struct DevModel {
   // ---- sizes
   int nq, nv, nu, na, nbody, njnt, ngeom, nsite, nten, nwrap, nM;
+  int nsensor;                                 // touch sensors
+  const int *sens_site, *sens_body, *sens_type; // [nsensor]: site id, its body, site shape (mjtGeom)
+  const float *sens_size;                      // [nsensor,3]
   int nframe, nlevel, nroot, ndlevel;
   int nunit, nslot, nentry, nnz;
   int ncg, npair, neq, nlimj, nlimt;

@@ -528,6 +528,19 @@ void myo_build_plan(const myo_model_desc& m, int nconmax_req, int njmax_req, Dev
       }
       doExplicit(1 << 30);
     }
+    {   // touch sensors: zone = the site's shape (box or sphere; the leg model's zones are boxes)
+      std::vector<int> ss, sb, st; std::vector<float> sz;
+      for (int i = 0; i < m.nsensor; i++) {
+        const int sid = m.sensor_objid[i];
+        if (sid < 0 || sid >= m.nsite) throw std::string("touch sensor refers to an unknown site");
+        const int ty = m.site_type[sid];
+        if (ty != 6 && ty != 2) throw std::string("unsupported touch-sensor zone (site type must be box or sphere)");
+        ss.push_back(sid); sb.push_back(m.site_bodyid[sid]); st.push_back(ty);
+        for (int k = 0; k < 3; k++) sz.push_back((float)m.site_size[3 * sid + k]);
+      }
+      D.nsensor = m.nsensor;
+      D.sens_site = upload(ss, owned); D.sens_body = upload(sb, owned); D.sens_type = upload(st, owned); D.sens_size = upload(sz, owned);
+    }
     D.ncg = (int)cg_geom.size(); D.npair = (int)p1.size();
     D.cg_geom = upload(cg_geom, owned); D.cg_type = upload(cg_type, owned); D.cg_frame = upload(cg_frame, owned); D.cg_body = upload(cg_body, owned);
     D.cg_lpos = upload(cg_lpos, owned); D.cg_lmat = upload(cg_lmat, owned); D.cg_size = upload(cg_size, owned); D.cg_rbound = upload(cg_rbound, owned);

@@ -1809,6 +1809,58 @@ __device__ __forceinline__ bool anyBad(SP v, int n, Tm t) {
   TFOR(i, n) bad |= !(fabsf(v[i]) < 1e10f);
   return teamAny(t, bad);
 }
+// ------------------------------------------------------------------------------------------ touch sensors (mj_sensorAcc)
+// sensordata[s] = sum of the normal forces of the active contacts that involve the sensor site's body and whose
+// normal ray (from the contact point, pointing into that body's side) meets the site's zone.  The pyramidal normal
+// force is the sum of the contact's row forces (mju_decodePyramid).
+__device__ __noinline__ void touchSensors(int slot, int fslot, SP sm, Tm t, World W, int ncon) {
+  const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L; const FieldPtrs& F = tP[fslot].F;
+  void* out = F.p[MYO_F_SENSORDATA];
+  if (!out) return;
+  TFOR(s, D.nsensor) {
+    const int sid = D.sens_site[s], body = D.sens_body[s], f = D.site_frame[sid];
+    const f3 spos = ld3(FR_POS(sm, L, f)) + mulM(FR_MAT(sm, L, f), ld3(D.site_lpos + 3 * sid));
+    float R[9]; mulMM(R, FR_MAT(sm, L, f), D.site_lmat + 9 * sid);
+    const f3 size = ld3(D.sens_size + 3 * s);
+    float total = 0.f;
+    for (int c = 0; c < ncon; c++) {
+      auto cr = sm + L.con + 12 * c;
+      const int adr = __float_as_int(cr[8]), dim = __float_as_int(cr[9]), pr = __float_as_int(cr[7]);
+      if (adr < 0) continue;
+      const int b1 = D.cg_body[D.pair_cg1[pr]], b2 = D.cg_body[D.pair_cg2[pr]];
+      if (body != b1 && body != b2) continue;
+      float fn = 0.f;
+      const int rows = dim == 1 ? 1 : 2 * (dim - 1);
+      for (int q = 0; q < rows; q++) fn += EFC(E_FORCE, adr + q);
+      if (!(fn > 0.f)) continue;
+      f3 dir = unit3(ld3(cr + 4) * fn);
+      if (body == b2) dir = dir * -1.f;
+      const f3 p = mulMT(R, ld3(cr + 1) - spos), v = mulMT(R, dir);   // ray in the site's frame
+      bool hit;
+      if (D.sens_type[s] == G_SPHERE) {
+        const float b = dot(p, v), cc = dot(p, p) - size.x * size.x, disc = b * b - cc;
+        hit = disc >= 0.f && (-b + sqrtf(disc)) >= 0.f;
+      } else {   // box: slab test, the ray t >= 0 meets the solid box
+        float t0 = 0.f, t1 = 3.4e38f;
+        const float pp[3] = {p.x, p.y, p.z}, vv[3] = {v.x, v.y, v.z}, hh[3] = {size.x, size.y, size.z};
+        hit = true;
+        for (int k = 0; k < 3; k++) {
+          if (fabsf(vv[k]) < MINVAL) { if (fabsf(pp[k]) > hh[k]) hit = false; }
+          else {
+            const float inv = 1.f / vv[k];
+            float a = (-hh[k] - pp[k]) * inv, b = (hh[k] - pp[k]) * inv;
+            if (a > b) { const float tmp = a; a = b; b = tmp; }
+            t0 = fmaxf(t0, a); t1 = fminf(t1, b);
+          }
+        }
+        hit = hit && t0 <= t1;
+      }
+      if (hit) total += fn;
+    }
+    OUTF(out, s) = total;
+  }
+}
+
 __device__ __noinline__ void resetState(int slot, SP sm, Tm t) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
   TFOR(i, D.nq) sm[L.qpos + i] = D.qpos0[i];
@@ -1948,6 +2000,7 @@ __global__ void __launch_bounds__(32 * CTA_WARPS, CTA_MINBLOCKS) stepKernel(int 
     }
     if (live && last && !posvel) {
       writeConstraintOutputs(slot, fslot, sm, t, W, ncon, nefc, niter);
+      if (D.nsensor > 0) touchSensors(slot, fslot, sm, t, W, nefc > 0 ? ncon : 0);
       void* o;
       if ((o = F.p[MYO_F_QACC])) TFOR(i, nv) OUTF(o, i) = sm[L.qacc + i];
       if ((o = F.p[MYO_F_QFRC_CONSTRAINT])) TFOR(i, nv) OUTF(o, i) = sm[L.qfrc_con + i];

@@ -416,7 +416,7 @@ template <typename T> struct Oracle {
   std::vector<T> xpos, xquat, xmat, xipos, ximat, xanchor, xaxis, geom_xpos, geom_xmat, site_xpos, site_xmat, subtree_com,
       cinert, crb, cdof, cdof_dot, cvel, ten_length, ten_velocity, ten_J, wrap_xpos, actuator_length, actuator_velocity,
       actuator_moment, actuator_force, act_dot, qM, qLD, qLDiagInv, qMdense, qLDdense, qfrc_bias, qfrc_passive, qfrc_spring,
-      qfrc_damper, qfrc_actuator, qfrc_smooth, qfrc_constraint, qfrc_inverse, qacc, qacc_smooth, qfrc_applied;
+      qfrc_damper, qfrc_actuator, qfrc_smooth, qfrc_constraint, qfrc_inverse, qacc, qacc_smooth, qfrc_applied, sensordata;
   std::vector<int32_t> ten_wrapadr, ten_wrapnum, wrap_obj;
   std::vector<Contact<T>> contacts;
   // exported flat contact / efc arrays
@@ -442,6 +442,7 @@ template <typename T> struct Oracle {
     qLD.assign(nM, 0); qLDiagInv.assign(nv, 0); qMdense.assign((size_t)nv * nv, 0); qLDdense.assign((size_t)nv * nv, 0);
     for (auto* v : {&qfrc_bias, &qfrc_passive, &qfrc_spring, &qfrc_damper, &qfrc_actuator, &qfrc_smooth, &qfrc_constraint,
                     &qfrc_inverse, &qacc, &qacc_smooth, &qfrc_applied}) v->assign(nv, 0);
+    sensordata.assign(m.nsensor, 0);
     ncon_v.assign(1, 0); nefc_v.assign(1, 0); solver_niter.assign(1, 0); status.assign(1, 0); solver_cost.assign(1, 0);
     reset();
 #define REG(f) fields[#f] = {(void*)f.data(), {(int64_t)f.size(), 0}}
@@ -453,7 +454,7 @@ template <typename T> struct Oracle {
     REG(qLDiagInv); REG(qMdense); REG(qLDdense); REG(qfrc_bias); REG(qfrc_passive); REG(qfrc_spring); REG(qfrc_damper);
     REG(qfrc_actuator); REG(qfrc_applied); REG(qfrc_smooth); REG(qfrc_constraint); REG(qfrc_inverse); REG(qacc); REG(qacc_smooth);
     REGI(ten_wrapadr); REGI(ten_wrapnum); REGI(wrap_obj); REGI(ncon_v); REGI(nefc_v); REGI(solver_niter); REGI(status);
-    REG(solver_cost);
+    REG(solver_cost); REG(sensordata);
   }
   void regDyn() {  // vectors whose size changes per step
     REGI(contact_geom); REGI(contact_dim); REGI(contact_efc_address); REGI(efc_type);
@@ -1343,7 +1344,57 @@ template <typename T> struct Oracle {
     kinematics(); comPos(); tendon(); crbM(); factorM(); collision(); makeConstraint(); transmission();
     fwdVelocity(); fwdActuation(); fwdAcceleration(); fwdConstraint();
     for (int i = 0; i < nv; i++) qfrc_inverse[i] = 0;
+    sensorTouch();
     exportContacts();
+  }
+
+  // mj_sensorAcc, mjSENS_TOUCH (MuJoCo 3.2.8 engine_sensor.c semantics): for every active contact that involves the
+  // sensor site's body, normal force = first component of mj_contactForce (pyramidal: the sum of the contact's row
+  // forces, mju_decodePyramid); it is added when positive and when the ray from the contact point along the normal
+  // (flipped if the site's body is the contact's second body) meets the site's zone (mju_rayGeom >= 0).
+  void sensorTouch() {
+    for (int s = 0; s < m.nsensor; s++) {
+      const int sid = m.sensor_objid[s], body = m.site_bodyid[sid], type = m.site_type[sid];
+      const T* sp = &site_xpos[3 * sid]; const T* R = &site_xmat[9 * sid];
+      const double* size = m.site_size + 3 * sid;
+      T total = 0;
+      for (const Contact<T>& c : contacts) {
+        if (c.efc_address < 0) continue;
+        const int b1 = m.geom_bodyid[c.geom1], b2 = m.geom_bodyid[c.geom2];
+        if (body != b1 && body != b2) continue;
+        const int rows = c.dim == 1 ? 1 : 2 * (c.dim - 1);
+        T fn = 0;
+        for (int q = 0; q < rows; q++) fn += efc_force[c.efc_address + q];
+        if (!(fn > 0)) continue;
+        T dir[3] = {c.frame[0] * fn, c.frame[1] * fn, c.frame[2] * fn};
+        const T nn = std::sqrt(dir[0] * dir[0] + dir[1] * dir[1] + dir[2] * dir[2]);
+        for (int k = 0; k < 3; k++) dir[k] = nn < T(1e-15) ? T(k == 0) : dir[k] / nn;
+        if (body == b2) for (int k = 0; k < 3; k++) dir[k] = -dir[k];
+        T p[3], v[3];
+        for (int k = 0; k < 3; k++) {   // ray in the site frame: R^T (x - site_xpos)
+          p[k] = R[k] * (c.pos[0] - sp[0]) + R[3 + k] * (c.pos[1] - sp[1]) + R[6 + k] * (c.pos[2] - sp[2]);
+          v[k] = R[k] * dir[0] + R[3 + k] * dir[1] + R[6 + k] * dir[2];
+        }
+        bool hit = true;
+        if (type == 2) {          // sphere
+          const T b = p[0] * v[0] + p[1] * v[1] + p[2] * v[2], cc = p[0] * p[0] + p[1] * p[1] + p[2] * p[2] - T(size[0] * size[0]), disc = b * b - cc;
+          hit = disc >= 0 && (-b + std::sqrt(disc)) >= 0;
+        } else {                  // box (validated at plan time by the library; the oracle supports the same two shapes)
+          T t0 = 0, t1 = std::numeric_limits<T>::max();
+          for (int k = 0; k < 3; k++) {
+            if (std::fabs(v[k]) < T(1e-15)) { if (std::fabs(p[k]) > T(size[k])) hit = false; }
+            else {
+              T a = (T(-size[k]) - p[k]) / v[k], b = (T(size[k]) - p[k]) / v[k];
+              if (a > b) std::swap(a, b);
+              t0 = std::max(t0, a); t1 = std::min(t1, b);
+            }
+          }
+          hit = hit && t0 <= t1;
+        }
+        if (hit) total += fn;
+      }
+      sensordata[s] = total;
+    }
   }
 
   bool bad(const std::vector<T>& v) const {

@@ -122,6 +122,36 @@ def test_bounded_drift_1000_steps(models, name):
     assert np.all(got.status == 0)
 
 
+def test_touch_sensors_match_oracle(models):
+    """mj_sensorAcc touch sensors of the leg model: a standing pose dropped a little onto the ground, then
+    forward passes of the GPU and the oracle from the same state.  Tolerance: rel 2e-3 of the largest reading (the
+    readings are sums of float32 Newton forces); which sensors fire must agree."""
+    import oracle
+    m = models("legs")
+    assert m.nsensor == 4
+    nw = 8
+    rng = np.random.default_rng(3)
+    key = np.asarray(m.key_qpos, dtype=np.float64)[0]
+    qpos = np.tile(key, (nw, 1)); qpos[:, 7:] += rng.normal(size=(nw, m.nq - 7)) * 0.02
+    qvel = np.zeros((nw, m.nv)); act = np.zeros((nw, m.na)); ctrl = rng.uniform(0, 0.3, size=(nw, m.nu))
+    o = oracle.Oracle(m)
+    states = []
+    for w in range(nw):       # settle on the ground with the oracle, then compare forward passes from that state
+        o.reset(); o.set_state(qpos[w], qvel[w], act[w], ctrl[w]); o.step(120 + 10 * w)
+        states.append((o.qpos.copy(), o.qvel.copy(), o.act.copy(), o.qacc_warmstart.copy()))
+    q = np.stack([s[0] for s in states]); v = np.stack([s[1] for s in states]); a = np.stack([s[2] for s in states]); ws = np.stack([s[3] for s in states])
+    model, d, got = parity.gpu_forward(m, q, v, a, ctrl, warm=ws)
+    ref = []
+    for w in range(nw):
+        o.set_state(q[w], v[w], a[w], ctrl[w], ws[w]); o.forward(); ref.append(np.array(o.sensordata))
+    ref = np.stack(ref)
+    assert ref.max() > 50.0 and (ref > 0).sum() >= nw          # the feet carry the body
+    assert np.array_equal(got.sensordata > 0, ref > 0)
+    assert np.abs(got.sensordata - ref).max() < 2e-3 * ref.max()
+    total_normal = np.array([sum(max(0.0, float(x)) for x in r) for r in ref])
+    assert (total_normal < 3.0 * 9.81 * float(np.sum(m.body_mass))).all()
+
+
 def test_fused_substeps_equal_repeated_steps(models):
     import torch
     from myosuite_mjx_b200 import mjx
