@@ -250,12 +250,15 @@ int myo_step_host(myo_batch *b, int nsubsteps, const float *qpos, const float *q
  * sequence does not depend on the batch size or on the number of GPUs.  All env buffers are caller-owned device
  * memory in the [k][nworld] layout, bound with myo_env_bind. */
 enum { MYO_COND_NONE = 0, MYO_COND_SARCOPENIA = 1, MYO_COND_FATIGUE = 2, MYO_COND_REAFFERENTATION = 3 };
-enum { MYO_ENV_POSE = 0, MYO_ENV_WALK = 1 };   /* PoseEnvV0 (pose_v0.py) / WalkEnvV0 (walk_v0.py) */
+enum { MYO_ENV_POSE = 0, MYO_ENV_WALK = 1, MYO_ENV_REORIENT = 2 };   /* PoseEnvV0 (pose_v0.py), WalkEnvV0 (walk_v0.py), ProprioceptiveEnvV0 (reorient_sar_v0.py) */
 enum {   /* obs_dict keys: pose_v0.py:106-116, walk_v0.py:263-283 */
   MYO_OBS_TIME = 0, MYO_OBS_QPOS = 1, MYO_OBS_QVEL = 2, MYO_OBS_ACT = 3, MYO_OBS_POSE_ERR = 4,
   MYO_OBS_QPOS_WITHOUT_XY = 5, MYO_OBS_COM_VEL = 6, MYO_OBS_TORSO_ANGLE = 7, MYO_OBS_FEET_HEIGHTS = 8, MYO_OBS_HEIGHT = 9,
   MYO_OBS_FEET_REL_POSITIONS = 10, MYO_OBS_PHASE_VAR = 11, MYO_OBS_MUSCLE_LENGTH = 12, MYO_OBS_MUSCLE_VELOCITY = 13,
-  MYO_OBS_MUSCLE_FORCE = 14
+  MYO_OBS_MUSCLE_FORCE = 14,
+  /* reorient_sar_v0.py:115-137 */
+  MYO_OBS_HAND_JNT = 15, MYO_OBS_OBJ_POS = 16, MYO_OBS_OBJ_VEL = 17, MYO_OBS_OBJ_ROT = 18, MYO_OBS_OBJ_DES_ROT = 19,
+  MYO_OBS_OBJ_ERR_POS = 20, MYO_OBS_OBJ_ERR_ROT = 21, MYO_OBS_MLEN = 22, MYO_OBS_MVEL = 23, MYO_OBS_MFORCE = 24
 };
 #define MYO_MAX_OBS_KEYS 16
 enum { MYO_TARGET_FIXED = 0, MYO_TARGET_GENERATE = 1 };
@@ -263,6 +266,8 @@ enum { MYO_RESET_INIT = 0, MYO_RESET_RANDOM = 1 };
 /* slots of MYO_E_RWD_TERMS.  pose: pose, bonus, penalty, act_reg, sparse, solved, done, -.
  * walk (walk_v0.py:297-310): vel_reward, cyclic_hip, ref_rot, joint_angle_rew, act_mag, sparse, solved, done. */
 enum { MYO_RWD_POSE = 0, MYO_RWD_BONUS, MYO_RWD_PENALTY, MYO_RWD_ACT_REG, MYO_RWD_SPARSE, MYO_RWD_SOLVED, MYO_RWD_DONE, MYO_RWD_SPARE, MYO_RWD_COUNT };
+/* reorient (reorient_sar_v0.py:139-168): pos_align, rot_align, act_reg, drop, bonus, sparse, solved, done */
+enum { MYO_RWD_R_POS_ALIGN = 0, MYO_RWD_R_ROT_ALIGN, MYO_RWD_R_ACT_REG, MYO_RWD_R_DROP, MYO_RWD_R_BONUS, MYO_RWD_R_SPARSE, MYO_RWD_R_SOLVED, MYO_RWD_R_DONE };
 enum { MYO_RWD_W_VEL = 0, MYO_RWD_W_CYCLIC_HIP, MYO_RWD_W_REF_ROT, MYO_RWD_W_JOINT_ANGLE, MYO_RWD_W_ACT_MAG, MYO_RWD_W_SPARSE, MYO_RWD_W_SOLVED, MYO_RWD_W_DONE };
 
 typedef enum myo_env_field {
@@ -304,6 +309,13 @@ typedef struct myo_env_desc {
   float w_vel, w_done, w_cyclic, w_ref_rot, w_joint_angle;
   const float *body_mass;                                  /* [nbody] */
   const float *alt_qpos, *alt_qvel;                        /* [nq], [nv]: second start state of reset_type random (key 3) */
+  /* ---- kind == MYO_ENV_REORIENT (myosuite/envs/myo/myobase/reorient_sar_v0.py:67-173).  Needs xpos, site_xpos, geom_xpos,
+   * actuator_length / velocity / force bound on the batch.  MYO_E_TARGET holds obj_des_rot [3] per world: the XML's target
+   * pose (target_value) or, with target_type generate, the orientation drawn at reset as Geometries8EnvV0.reset does
+   * (euler (U(-1,1), U(-0.8,1.2), 0) -> quat, :251-257) applied to the target's top - bottom axis (target_axis). */
+  int32_t obj_bid, eps_ball_sid, obj_top_gid, obj_bot_gid;
+  float pen_length, tar_length, target_axis[3];
+  float w_pos_align, w_rot_align, w_r_act_reg, w_drop, w_r_bonus;
 } myo_env_desc;
 
 typedef struct myo_env myo_env;

@@ -35,6 +35,10 @@ struct EnvParams {
   int kind, nbody, foot_l, foot_r, pelvis, torso, hip_flex[2], hip_angle[4];
   float min_height, max_rot, hip_period, target_x_vel, target_y_vel, target_rot[4], reset_noise, w_vel, w_done, w_cyclic, w_ref_rot, w_joint_angle;
   const float *xpos, *xquat, *xipos, *cvel, *actlen, *actvel, *actfrc;   // bound derived fields the walk observation reads
+  // reorient env
+  int obj_bid, eps_sid, top_gid, bot_gid;
+  float pen_length, tar_length, target_axis[3], w_pos_align, w_rot_align, w_r_act_reg, w_drop, w_r_bonus;
+  const float *site_xpos, *geom_xpos;
   int* reset_mask;   // [nworld], library-owned: worlds reset by the last step (they need a full mj_forward)
 };
 
@@ -106,6 +110,23 @@ __device__ void envResetWorld(const EnvParams& P, size_t w) {
   const size_t nw = (size_t)P.nworld;
   const unsigned gw = (unsigned)(P.world_offset + (int)w);
   const unsigned ep = (unsigned)EI(MYO_E_EPISODE, 0);
+  if (P.kind == MYO_ENV_REORIENT) {
+    // obj_des_rot: the XML's target axis, or a fresh desired orientation (reorient_sar_v0.py:251-257: euler (U(-1,1),
+    // U(-0.8,1.2), 0) -> quat by myosuite/utils/quat_math.py:77-93, applied to the target's top - bottom axis)
+    float d[3] = {P.T.target_value[0], P.T.target_value[1], P.T.target_value[2]};
+    if (P.target_type == MYO_TARGET_GENERATE) {
+      const float e0 = __fadd_rn(-1.0f, __fmul_rn(2.0f, envUniform(P.seed, gw, ep, 0u, 0u))), e1 = __fadd_rn(-0.8f, __fmul_rn(2.0f, envUniform(P.seed, gw, ep, 0u, 1u)));
+      const float ai = 0.f, aj = -0.5f * e1, ak = 0.5f * e0;
+      const float si = sinf(ai), sj = sinf(aj), sk = sinf(ak), ci = cosf(ai), cj = cosf(aj), ck = cosf(ak);
+      const float cc = ci * ck, cs = ci * sk, sc = si * ck, ss = si * sk;
+      const float qw = cj * cc + sj * ss, qz = cj * sc - sj * cs, qy = -(cj * ss + sj * cc), qx = cj * cs - sj * sc;
+      const float ax = P.target_axis[0], ay = P.target_axis[1], az = P.target_axis[2];
+      // rotate the axis by the unit quaternion: v + 2 q_v x (q_v x v + w v)
+      const float tx = qy * az - qz * ay + qw * ax, ty = qz * ax - qx * az + qw * ay, tz = qx * ay - qy * ax + qw * az;
+      d[0] = (ax + 2.f * (qy * tz - qz * ty)) / P.tar_length; d[1] = (ay + 2.f * (qz * tx - qx * tz)) / P.tar_length; d[2] = (az + 2.f * (qx * ty - qy * tx)) / P.tar_length;
+    }
+    for (int k = 0; k < 3; k++) EF(MYO_E_TARGET, k) = d[k];
+  } else
   for (int k = 0; k < P.ntarget; k++) {
     float t;
     if (P.target_type == MYO_TARGET_GENERATE) {
@@ -191,6 +212,17 @@ __device__ void envWriteObs(const EnvParams& P, size_t w) {
       case MYO_OBS_MUSCLE_LENGTH: for (int j = 0; j < P.nu; j++) EF(MYO_E_OBS, o++) = ST(P.actlen, j); break;
       case MYO_OBS_MUSCLE_VELOCITY: for (int j = 0; j < P.nu; j++) EF(MYO_E_OBS, o++) = fminf(fmaxf(ST(P.actvel, j), -100.f), 100.f); break;
       case MYO_OBS_MUSCLE_FORCE: for (int j = 0; j < P.nu; j++) EF(MYO_E_OBS, o++) = fminf(fmaxf(ST(P.actfrc, j) / 1000.f, -100.f), 100.f); break;
+      // ---- reorient_sar_v0.py:115-137
+      case MYO_OBS_HAND_JNT: for (int j = 0; j < P.nq - 6; j++) EF(MYO_E_OBS, o++) = ST(P.qpos, j); break;
+      case MYO_OBS_OBJ_POS: for (int k = 0; k < 3; k++) EF(MYO_E_OBS, o++) = ST(P.xpos, 3 * P.obj_bid + k); break;
+      case MYO_OBS_OBJ_VEL: for (int j = P.nv - 6; j < P.nv; j++) EF(MYO_E_OBS, o++) = ST(P.qvel, j) * P.dt; break;
+      case MYO_OBS_OBJ_ROT: for (int k = 0; k < 3; k++) EF(MYO_E_OBS, o++) = (ST(P.geom_xpos, 3 * P.top_gid + k) - ST(P.geom_xpos, 3 * P.bot_gid + k)) / P.pen_length; break;
+      case MYO_OBS_OBJ_DES_ROT: for (int k = 0; k < 3; k++) EF(MYO_E_OBS, o++) = EF(MYO_E_TARGET, k); break;
+      case MYO_OBS_OBJ_ERR_POS: for (int k = 0; k < 3; k++) EF(MYO_E_OBS, o++) = ST(P.xpos, 3 * P.obj_bid + k) - ST(P.site_xpos, 3 * P.eps_sid + k); break;
+      case MYO_OBS_OBJ_ERR_ROT: for (int k = 0; k < 3; k++) EF(MYO_E_OBS, o++) = (ST(P.geom_xpos, 3 * P.top_gid + k) - ST(P.geom_xpos, 3 * P.bot_gid + k)) / P.pen_length - EF(MYO_E_TARGET, k); break;
+      case MYO_OBS_MLEN: for (int j = 0; j < P.nu; j++) EF(MYO_E_OBS, o++) = ST(P.actlen, j); break;
+      case MYO_OBS_MVEL: for (int j = 0; j < P.nu; j++) EF(MYO_E_OBS, o++) = ST(P.actvel, j); break;
+      case MYO_OBS_MFORCE: for (int j = 0; j < P.nu; j++) EF(MYO_E_OBS, o++) = ST(P.actfrc, j); break;
     }
   }
 }
@@ -267,6 +299,39 @@ __global__ void __launch_bounds__(128) envWalkRewardKernel(const EnvParams P, co
   if (reset) envResetWorld(P, w);
   if (P.reset_mask) P.reset_mask[w] = reset ? 1 : 0;
 }
+// ---- reorient: reward terms, done, reset decision (reorient_sar_v0.py:139-168); one thread per world, after the refresh
+__global__ void __launch_bounds__(128) envReorientRewardKernel(const EnvParams P, const int advance) {
+  const size_t nw = (size_t)P.nworld;
+  const size_t w = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (w >= nw) return;
+  float e2 = 0.f, dotv = 0.f, n1 = 0.f, n2 = 0.f;
+  for (int k = 0; k < 3; k++) {
+    const float e = ST(P.xpos, 3 * P.obj_bid + k) - ST(P.site_xpos, 3 * P.eps_sid + k); e2 = fmaf(e, e, e2);
+    const float r = (ST(P.geom_xpos, 3 * P.top_gid + k) - ST(P.geom_xpos, 3 * P.bot_gid + k)) / P.pen_length, d = EF(MYO_E_TARGET, k);
+    dotv = fmaf(r, d, dotv); n1 = fmaf(r, r, n1); n2 = fmaf(d, d, n2);
+  }
+  const float pos_align = sqrtf(e2);
+  const float rot_align = dotv / (sqrtf(n1) * sqrtf(n2));   // calculate_cosine, myosuite/utils/vector_math.py:11-36
+  const bool dropped = pos_align > 0.075f;
+  float a2 = 0.f;
+  for (int j = 0; j < P.na; j++) { const float a = ST(P.act, j); a2 = fmaf(a, a, a2); }
+  const float act_mag = P.na != 0 ? sqrtf(a2) / (float)P.na : 0.f;
+  const float close = pos_align < 0.075f ? 1.f : 0.f;
+  const float bonus = 1.0f * (rot_align > 0.9f ? 1.f : 0.f) * close + 5.0f * (rot_align > 0.95f ? 1.f : 0.f) * close;
+  EF(MYO_E_RWD_TERMS, MYO_RWD_R_POS_ALIGN) = -pos_align; EF(MYO_E_RWD_TERMS, MYO_RWD_R_ROT_ALIGN) = rot_align; EF(MYO_E_RWD_TERMS, MYO_RWD_R_ACT_REG) = -act_mag;
+  EF(MYO_E_RWD_TERMS, MYO_RWD_R_DROP) = dropped ? -1.f : 0.f; EF(MYO_E_RWD_TERMS, MYO_RWD_R_BONUS) = bonus;
+  EF(MYO_E_RWD_TERMS, MYO_RWD_R_SPARSE) = -pos_align + rot_align;
+  EF(MYO_E_RWD_TERMS, MYO_RWD_R_SOLVED) = (rot_align > 0.95f && !dropped) ? 1.f : 0.f; EF(MYO_E_RWD_TERMS, MYO_RWD_R_DONE) = dropped ? 1.f : 0.f;
+  // dense in the order of DEFAULT_RWD_KEYS_AND_WEIGHTS (reorient_sar_v0.py:37-43): pos_align, rot_align, act_reg, drop, bonus
+  EF(MYO_E_REWARD, 0) = (((P.w_pos_align * -pos_align + P.w_rot_align * rot_align) + P.w_r_act_reg * -act_mag) + P.w_drop * (dropped ? -1.f : 0.f)) + P.w_r_bonus * bonus;
+  const int steps = EI(MYO_E_STEPS, 0) + advance;
+  if (advance) EI(MYO_E_STEPS, 0) = steps;
+  const bool ended = dropped || (P.horizon > 0 && steps >= P.horizon);
+  EF(MYO_E_DONE, 0) = ended ? 1.f : 0.f;
+  const bool reset = ended && advance && P.auto_reset;
+  if (reset) envResetWorld(P, w);
+  if (P.reset_mask) P.reset_mask[w] = reset ? 1 : 0;
+}
 __global__ void __launch_bounds__(128) envObsKernel(const EnvParams P) {
   const size_t w = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (w >= (size_t)P.nworld) return;
@@ -281,7 +346,7 @@ __global__ void __launch_bounds__(128) envResetKernel(const EnvParams P, const i
   envResetWorld(P, w);
   EF(MYO_E_REWARD, 0) = 0.f; EF(MYO_E_DONE, 0) = 0.f;
   for (int k = 0; k < MYO_RWD_COUNT; k++) EF(MYO_E_RWD_TERMS, k) = 0.f;
-  if (P.kind == MYO_ENV_POSE) envWriteObs(P, w);   // the walk observation needs mj_forward of the new state first
+  if (P.kind == MYO_ENV_POSE) envWriteObs(P, w);   // the walk / reorient observations need mj_forward of the new state first
 }
 
 template <class T> const T* toDevice(const T* host, size_t n, std::vector<void*>& owned) {
@@ -312,7 +377,13 @@ int myo_env_create(myo_batch* b, const myo_env_desc* d, myo_env** out) {
   const DevModel& D = b->D;
   if (d->frame_skip < 1) return myo_fail(MYO_ERR_ARG, "frame_skip must be >= 1");
   if (d->nobs_keys < 0 || d->nobs_keys > MYO_MAX_OBS_KEYS) return myo_fail(MYO_ERR_ARG, "too many obs keys");
-  if (d->kind != MYO_ENV_POSE && d->kind != MYO_ENV_WALK) return myo_fail(MYO_ERR_ARG, "unknown env kind");
+  if (d->kind != MYO_ENV_POSE && d->kind != MYO_ENV_WALK && d->kind != MYO_ENV_REORIENT) return myo_fail(MYO_ERR_ARG, "unknown env kind");
+  if (d->kind == MYO_ENV_REORIENT) {
+    if (D.nq < 7 || D.nv < 6) return myo_fail(MYO_ERR_ARG, "the reorient env needs an object with six trailing coordinates");
+    if (d->obj_bid < 0 || d->obj_bid >= D.nbody || d->eps_ball_sid < 0 || d->eps_ball_sid >= D.nsite || d->obj_top_gid < 0 || d->obj_top_gid >= D.ngeom ||
+        d->obj_bot_gid < 0 || d->obj_bot_gid >= D.ngeom) return myo_fail(MYO_ERR_ARG, "reorient body / site / geom id out of range");
+    if (!(d->pen_length > 0.f) || !(d->tar_length > 0.f) || d->ntarget != 3 || !d->target_value) return myo_fail(MYO_ERR_ARG, "reorient target description missing");
+  }
   if (d->kind == MYO_ENV_WALK) {
     if (D.nq < 7 || !d->body_mass) return myo_fail(MYO_ERR_ARG, "the walk env needs a free root joint and body_mass");
     if (d->reset_type == MYO_RESET_RANDOM && (!d->alt_qpos || !d->alt_qvel)) return myo_fail(MYO_ERR_ARG, "alt_qpos / alt_qvel missing");
@@ -322,8 +393,8 @@ int myo_env_create(myo_batch* b, const myo_env_desc* d, myo_env** out) {
     for (int k = 0; k < 4; k++) if (d->hip_angle_adr[k] < 0 || d->hip_angle_adr[k] >= D.nq) return myo_fail(MYO_ERR_ARG, "hip_angle_adr out of range");
     if (!(d->hip_period > 0.f)) return myo_fail(MYO_ERR_ARG, "hip_period must be positive");
   }
-  if (d->ntarget < 0 || (d->ntarget > 0 && !d->target_qposadr)) return myo_fail(MYO_ERR_ARG, "target_qposadr missing");
-  if (d->target_type == MYO_TARGET_GENERATE && d->ntarget > 0 && !d->target_range) return myo_fail(MYO_ERR_ARG, "target_range missing");
+  if (d->ntarget < 0 || (d->kind == MYO_ENV_POSE && d->ntarget > 0 && !d->target_qposadr)) return myo_fail(MYO_ERR_ARG, "target_qposadr missing");
+  if (d->kind == MYO_ENV_POSE && d->target_type == MYO_TARGET_GENERATE && d->ntarget > 0 && !d->target_range) return myo_fail(MYO_ERR_ARG, "target_range missing");
   if (d->target_type == MYO_TARGET_FIXED && d->ntarget > 0 && !d->target_value) return myo_fail(MYO_ERR_ARG, "target_value missing");
   if (!d->init_qpos || !d->init_qvel) return myo_fail(MYO_ERR_ARG, "init_qpos / init_qvel missing");
   if (d->kind == MYO_ENV_POSE && d->reset_type == MYO_RESET_RANDOM && (!d->reset_lo || !d->reset_hi)) return myo_fail(MYO_ERR_ARG, "reset range missing");
@@ -331,7 +402,8 @@ int myo_env_create(myo_batch* b, const myo_env_desc* d, myo_env** out) {
   if (d->muscle_condition == MYO_COND_FATIGUE && (!d->tau_act || !d->tau_deact)) return myo_fail(MYO_ERR_ARG, "tau_act / tau_deact missing");
   if (d->muscle_condition == MYO_COND_REAFFERENTATION && (d->epl_id < 0 || d->epl_id >= D.nu || d->eip_id < 0 || d->eip_id >= D.nu))
     return myo_fail(MYO_ERR_ARG, "reafferentation needs the EPL and EIP actuator ids");
-  for (int k = 0; k < d->ntarget; k++) if (d->target_qposadr[k] < 0 || d->target_qposadr[k] >= D.nq) return myo_fail(MYO_ERR_ARG, "target_qposadr out of range");
+  if (d->kind == MYO_ENV_POSE)
+    for (int k = 0; k < d->ntarget; k++) if (d->target_qposadr[k] < 0 || d->target_qposadr[k] >= D.nq) return myo_fail(MYO_ERR_ARG, "target_qposadr out of range");
   if (cudaSetDevice(b->model->device) != cudaSuccess) return myo_fail(MYO_ERR_CUDA, "cudaSetDevice failed: libmyostep has no CPU fallback");
   myo_env* e = new myo_env();
   e->b = b;
@@ -346,6 +418,9 @@ int myo_env_create(myo_batch* b, const myo_env_desc* d, myo_env** out) {
   P.pose_thd = d->pose_thd; P.far_th = d->far_th; P.w_pose = d->w_pose; P.w_bonus = d->w_bonus; P.w_act_reg = d->w_act_reg; P.w_penalty = d->w_penalty;
   P.fat_F = d->fatigue_F; P.fat_R = d->fatigue_R; P.fat_r = d->fatigue_r;
   P.kind = d->kind; P.nbody = D.nbody;
+  P.obj_bid = d->obj_bid; P.eps_sid = d->eps_ball_sid; P.top_gid = d->obj_top_gid; P.bot_gid = d->obj_bot_gid; P.pen_length = d->pen_length; P.tar_length = d->tar_length;
+  for (int k = 0; k < 3; k++) P.target_axis[k] = d->target_axis[k];
+  P.w_pos_align = d->w_pos_align; P.w_rot_align = d->w_rot_align; P.w_r_act_reg = d->w_r_act_reg; P.w_drop = d->w_drop; P.w_r_bonus = d->w_r_bonus;
   P.foot_l = d->foot_l_bid; P.foot_r = d->foot_r_bid; P.pelvis = d->pelvis_bid; P.torso = d->torso_bid;
   for (int k = 0; k < 2; k++) P.hip_flex[k] = d->hip_flex_adr[k];
   for (int k = 0; k < 4; k++) { P.hip_angle[k] = d->hip_angle_adr[k]; P.target_rot[k] = d->target_rot[k]; }
@@ -354,7 +429,8 @@ int myo_env_create(myo_batch* b, const myo_env_desc* d, myo_env** out) {
   for (int q = 0; q < d->nobs_keys; q++) {
     const int key = d->obs_keys[q];
     P.obs_keys[q] = key;
-    if (key >= MYO_OBS_QPOS_WITHOUT_XY && d->kind != MYO_ENV_WALK) { delete e; return myo_fail(MYO_ERR_ARG, "walk obs key on a pose env"); }
+    if (key >= MYO_OBS_QPOS_WITHOUT_XY && key <= MYO_OBS_MUSCLE_FORCE && d->kind != MYO_ENV_WALK) { delete e; return myo_fail(MYO_ERR_ARG, "walk obs key on another env kind"); }
+    if (key >= MYO_OBS_HAND_JNT && d->kind != MYO_ENV_REORIENT) { delete e; return myo_fail(MYO_ERR_ARG, "reorient obs key on another env kind"); }
     if (key == MYO_OBS_POSE_ERR && d->kind != MYO_ENV_POSE) { delete e; return myo_fail(MYO_ERR_ARG, "pose obs key on a walk env"); }
     switch (key) {
       case MYO_OBS_TIME: P.nobs += 1; break;
@@ -368,6 +444,10 @@ int myo_env_create(myo_batch* b, const myo_env_desc* d, myo_env** out) {
       case MYO_OBS_HEIGHT: case MYO_OBS_PHASE_VAR: P.nobs += 1; break;
       case MYO_OBS_FEET_REL_POSITIONS: P.nobs += 6; break;
       case MYO_OBS_MUSCLE_LENGTH: case MYO_OBS_MUSCLE_VELOCITY: case MYO_OBS_MUSCLE_FORCE: P.nobs += D.nu; break;
+      case MYO_OBS_HAND_JNT: P.nobs += D.nq - 6; break;
+      case MYO_OBS_OBJ_VEL: P.nobs += 6; break;
+      case MYO_OBS_OBJ_POS: case MYO_OBS_OBJ_ROT: case MYO_OBS_OBJ_DES_ROT: case MYO_OBS_OBJ_ERR_POS: case MYO_OBS_OBJ_ERR_ROT: P.nobs += 3; break;
+      case MYO_OBS_MLEN: case MYO_OBS_MVEL: case MYO_OBS_MFORCE: P.nobs += D.nu; break;
       default: delete e; return myo_fail(MYO_ERR_ARG, "unknown obs key");
     }
   }
@@ -391,6 +471,8 @@ int myo_env_create(myo_batch* b, const myo_env_desc* d, myo_env** out) {
       P.T.body_mass = toDevice(d->body_mass, D.nbody, e->owned);
       P.T.alt_qpos = toDevice(d->alt_qpos, D.nq, e->owned);
       P.T.alt_qvel = toDevice(d->alt_qvel, D.nv, e->owned);
+    }
+    if (d->kind != MYO_ENV_POSE) {
       void* m = nullptr;
       if (cudaMalloc(&m, (size_t)b->nworld * sizeof(int)) != cudaSuccess || cudaMemset(m, 0, (size_t)b->nworld * sizeof(int)) != cudaSuccess) throw std::string("cudaMalloc failed");
       e->owned.push_back(m); P.reset_mask = (int*)m;
@@ -436,8 +518,19 @@ static int envReady(myo_env* e) {
     if (!P.xpos || !P.xquat || !P.xipos || !P.cvel || !P.actlen || !P.actvel || !P.actfrc)
       return myo_fail(MYO_ERR_UNBOUND, "the walk env reads xpos, xquat, xipos, cvel, actuator_length, actuator_velocity and actuator_force: bind them on the batch");
   }
+  if (P.kind == MYO_ENV_REORIENT) {
+    P.xpos = (const float*)F.p[MYO_F_XPOS]; P.site_xpos = (const float*)F.p[MYO_F_SITE_XPOS]; P.geom_xpos = (const float*)F.p[MYO_F_GEOM_XPOS];
+    P.actlen = (const float*)F.p[MYO_F_ACTUATOR_LENGTH]; P.actvel = (const float*)F.p[MYO_F_ACTUATOR_VELOCITY]; P.actfrc = (const float*)F.p[MYO_F_ACTUATOR_FORCE];
+    if (!P.xpos || !P.site_xpos || !P.geom_xpos || !P.actlen || !P.actvel || !P.actfrc)
+      return myo_fail(MYO_ERR_UNBOUND, "the reorient env reads xpos, site_xpos, geom_xpos, actuator_length, actuator_velocity and actuator_force: bind them on the batch");
+  }
   if (cudaSetDevice(e->b->model->device) != cudaSuccess) return myo_fail(MYO_ERR_CUDA, "cudaSetDevice failed: libmyostep has no CPU fallback");
   return MYO_OK;
+}
+static void envRewardLaunch(const EnvParams& P, int advance, void* stream) {
+  if (P.kind == MYO_ENV_WALK) envWalkRewardKernel<<<(P.nworld + 127) / 128, 128, 0, (cudaStream_t)stream>>>(P, advance);
+  else envReorientRewardKernel<<<(P.nworld + 127) / 128, 128, 0, (cudaStream_t)stream>>>(P, advance);
+  myo_count_launch(1);
 }
 static int envLaunched() {
   return cudaPeekAtLastError() == cudaSuccess ? MYO_OK : myo_fail(MYO_ERR_CUDA, std::string("kernel launch failed: ") + cudaGetErrorString(cudaGetLastError()));
@@ -448,7 +541,7 @@ int myo_env_reset(myo_env* e, const int32_t* world_mask_dev, void* stream) {
   const EnvParams& P = e->P;
   envResetKernel<<<(P.nworld + 127) / 128, 128, 0, (cudaStream_t)stream>>>(P, world_mask_dev);
   myo_count_launch(1);
-  if (P.kind == MYO_ENV_WALK) {   // robot.reset ends with sim.forward() (robot.py:976-979); the observation reads its outputs
+  if (P.kind != MYO_ENV_POSE) {   // robot.reset ends with sim.forward() (robot.py:976-979); the observation reads its outputs
     rc = myo_forward_masked(e->b, world_mask_dev, stream);
     if (rc) return rc;
     envObsKernel<<<(P.nworld + 127) / 128, 128, 0, (cudaStream_t)stream>>>(P);
@@ -467,13 +560,12 @@ int myo_env_step(myo_env* e, void* stream) {
   }
   rc = myo_step(e->b, P.frame_skip, stream);
   if (rc) return rc;
-  if (P.kind == MYO_ENV_WALK) {
+  if (P.kind != MYO_ENV_POSE) {
     // classic-path observation semantics: position / velocity fields of the stepped state (dm_control Physics.step ends
     // with mj_step1), then reward / done / reset, a full mj_forward of the worlds that were reset, then the observation
     rc = myo_forward_posvel(e->b, nullptr, stream);
     if (rc) return rc;
-    envWalkRewardKernel<<<(P.nworld + 127) / 128, 128, 0, (cudaStream_t)stream>>>(P, 1);
-    myo_count_launch(1);
+    envRewardLaunch(P, 1, stream);
     if (P.auto_reset) {
       rc = myo_forward_masked(e->b, P.reset_mask, stream);
       if (rc) return rc;
@@ -489,10 +581,10 @@ int myo_env_step(myo_env* e, void* stream) {
 int myo_env_forward(myo_env* e, void* stream) {
   int rc = envReady(e);
   if (rc) return rc;
-  if (e->P.kind == MYO_ENV_WALK) {   // reads the derived fields as they are: call myo_forward / myo_forward_posvel first if the state was edited
-    envWalkRewardKernel<<<(e->P.nworld + 127) / 128, 128, 0, (cudaStream_t)stream>>>(e->P, 0);
+  if (e->P.kind != MYO_ENV_POSE) {   // reads the derived fields as they are: call myo_forward / myo_forward_posvel first if the state was edited
+    envRewardLaunch(e->P, 0, stream);
     envObsKernel<<<(e->P.nworld + 127) / 128, 128, 0, (cudaStream_t)stream>>>(e->P);
-    myo_count_launch(2);
+    myo_count_launch(1);
     return envLaunched();
   }
   envPostKernel<<<(e->P.nworld + 127) / 128, 128, 0, (cudaStream_t)stream>>>(e->P, 0);

@@ -15,12 +15,15 @@ from . import lib as _lib
 COND = {"": 0, None: 0, "none": 0, "sarcopenia": 1, "fatigue": 2, "reafferentation": 3}
 OBS_KEY = {"time": 0, "qpos": 1, "qvel": 2, "act": 3, "pose_err": 4, "qpos_without_xy": 5, "com_vel": 6, "torso_angle": 7,
            "feet_heights": 8, "height": 9, "feet_rel_positions": 10, "phase_var": 11, "muscle_length": 12, "muscle_velocity": 13,
-           "muscle_force": 14}
+           "muscle_force": 14, "hand_jnt": 15, "obj_pos": 16, "obj_vel": 17, "obj_rot": 18, "obj_des_rot": 19, "obj_err_pos": 20,
+           "obj_err_rot": 21, "mlen": 22, "mvel": 23, "mforce": 24}
 MAX_OBS_KEYS = 16
 E_FIELDS = ("action", "obs", "reward", "done", "rwd_terms", "target", "fatigue", "steps", "episode")
 E_INT = ("steps", "episode")
 RWD_TERMS = ("pose", "bonus", "penalty", "act_reg", "sparse", "solved", "done")
 WALK_RWD_TERMS = ("vel_reward", "cyclic_hip", "ref_rot", "joint_angle_rew", "act_mag", "sparse", "solved", "done")
+REORIENT_RWD_TERMS = ("pos_align", "rot_align", "act_reg", "drop", "bonus", "sparse", "solved", "done")
+REORIENT_FIELDS = ("xpos", "site_xpos", "geom_xpos", "actuator_length", "actuator_velocity", "actuator_force")
 WALK_FIELDS = ("xpos", "xquat", "xipos", "cvel", "actuator_length", "actuator_velocity", "actuator_force")   # what the walk obs reads
 
 _i32p, _f32p = ctypes.POINTER(ctypes.c_int32), ctypes.POINTER(ctypes.c_float)
@@ -43,7 +46,11 @@ class EnvDesc(ctypes.Structure):
                 ("min_height", ctypes.c_float), ("max_rot", ctypes.c_float), ("hip_period", ctypes.c_float), ("target_x_vel", ctypes.c_float),
                 ("target_y_vel", ctypes.c_float), ("target_rot", ctypes.c_float * 4), ("reset_noise", ctypes.c_float),
                 ("w_vel", ctypes.c_float), ("w_done", ctypes.c_float), ("w_cyclic", ctypes.c_float), ("w_ref_rot", ctypes.c_float),
-                ("w_joint_angle", ctypes.c_float), ("body_mass", _f32p), ("alt_qpos", _f32p), ("alt_qvel", _f32p)]
+                ("w_joint_angle", ctypes.c_float), ("body_mass", _f32p), ("alt_qpos", _f32p), ("alt_qvel", _f32p),
+                ("obj_bid", ctypes.c_int32), ("eps_ball_sid", ctypes.c_int32), ("obj_top_gid", ctypes.c_int32), ("obj_bot_gid", ctypes.c_int32),
+                ("pen_length", ctypes.c_float), ("tar_length", ctypes.c_float), ("target_axis", ctypes.c_float * 3),
+                ("w_pos_align", ctypes.c_float), ("w_rot_align", ctypes.c_float), ("w_r_act_reg", ctypes.c_float), ("w_drop", ctypes.c_float),
+                ("w_r_bonus", ctypes.c_float)]
 
 
 def _bind_protos(L):
@@ -147,6 +154,55 @@ def walk_config(mj, frame_skip=10, normalize_act=True, muscle_condition="", min_
     return base
 
 
+def _quat2mat(q):
+    w, x, y, z = q
+    return np.array([[1 - 2 * (y * y + z * z), 2 * (x * y - w * z), 2 * (x * z + w * y)], [2 * (x * y + w * z), 1 - 2 * (x * x + z * z), 2 * (y * z - w * x)],
+                     [2 * (x * z - w * y), 2 * (y * z + w * x), 1 - 2 * (x * x + y * y)]])
+
+
+def apply_reorient_setup(mj):
+    """ProprioceptiveEnvV0._setup edits the model before the first step: the object is 25 % heavier
+    (reorient_sar_v0.py:95).  Returns a copy of the host model to hand to put_model."""
+    import copy
+    m = copy.copy(mj)
+    mass = np.array(mj.body_mass, dtype=np.float64, copy=True)
+    mass[list(map(str, mj.names_body)).index("Object")] *= 1.25
+    m.body_mass = mass
+    return m
+
+
+def reorient_config(mj, frame_skip=5, normalize_act=True, muscle_condition="", randomize_target=True, obs_keys=None, weights=None, horizon=50,
+                    auto_reset=True, seed=0, world_offset=0, epl_id=-1, eip_id=-1):
+    """ProprioceptiveEnvV0 (reorient_sar_v0.py:67-173; registered with frame_skip 5 and a 50-step horizon, myobase/__init__.py:639-649).
+    `randomize_target` draws a desired orientation per episode as Geometries8EnvV0.reset does (:251-257); the per-episode
+    change of the object's SHAPE (:207-249) needs per-world model tables and is not reproduced: the object keeps the
+    XML's geometry."""
+    nb, ng, ns = [str(x) for x in mj.names_body], [str(x) for x in mj.names_geom], [str(x) for x in mj.names_site]
+    if obs_keys is None:
+        obs_keys = ["hand_jnt", "obj_pos", "obj_vel", "obj_rot", "obj_des_rot", "obj_err_pos", "obj_err_rot", "mlen", "mvel", "mforce"]   # :97-108
+    obs_keys = list(obs_keys)
+    if int(mj.na) > 0 and "act" not in obs_keys:
+        obs_keys.append("act")
+    w = dict(pos_align=1.0, rot_align=1.0, act_reg=5.0, drop=5.0, bonus=10.0)    # :37-43
+    w.update(weights or {})
+    gp = np.asarray(mj.geom_pos, dtype=np.float64)
+    top, bot, ttop, tbot = (ng.index(n) for n in ("top", "bot", "t_top", "t_bot"))
+    pen_length = float(np.linalg.norm(gp[top] - gp[bot])); tar_length = float(np.linalg.norm(gp[ttop] - gp[tbot]))
+    axis = gp[ttop] - gp[tbot]
+    tb = nb.index("target")
+    des = _quat2mat(np.asarray(mj.body_quat, dtype=np.float64)[tb]) @ axis / tar_length      # the XML's target pose (a child of the world body)
+    init_qpos = np.array(mj.qpos0, dtype=np.float32)
+    init_qpos[:-6] = 0.0; init_qpos[0] = -1.5                                               # :110-111: fully open, palm up
+    base = pose_config(mj, frame_skip=frame_skip, normalize_act=normalize_act, muscle_condition=muscle_condition, obs_keys=("qpos",), horizon=horizon,
+                       auto_reset=auto_reset, seed=seed, world_offset=world_offset, epl_id=epl_id, eip_id=eip_id, target_jnt_value=np.zeros(int(mj.nq)),
+                       init_qpos=init_qpos)
+    base.update(kind="reorient", obs_keys=obs_keys, reset_type="init", target_qposadr=np.zeros(3, np.int32), target_range=None,
+                target_value=des.astype(np.float32), target_type="generate" if randomize_target else "fixed",
+                obj_bid=nb.index("Object"), eps_ball_sid=ns.index("eps_ball"), top_gid=top, bot_gid=bot, pen_length=pen_length, tar_length=tar_length,
+                target_axis=axis.astype(np.float32), reorient_weights=(w["pos_align"], w["rot_align"], w["act_reg"], w["drop"], w["bonus"]))
+    return base
+
+
 class FusedEnv:
     """myo_env handle bound to a `mjx.Data` batch; env buffers are torch tensors in the [k, nworld] layout."""
 
@@ -182,6 +238,13 @@ class FusedEnv:
         d.act_is_muscle = arr(cfg["act_is_muscle"], np.int32)
         d.ctrl_lo, d.ctrl_hi = arr(cfg["ctrl_lo"], np.float32), arr(cfg["ctrl_hi"], np.float32)
         d.tau_act, d.tau_deact = arr(cfg["tau_act"], np.float32), arr(cfg["tau_deact"], np.float32)
+        if cfg.get("kind") == "reorient":
+            d.kind = 2
+            d.obj_bid, d.eps_ball_sid, d.obj_top_gid, d.obj_bot_gid = cfg["obj_bid"], cfg["eps_ball_sid"], cfg["top_gid"], cfg["bot_gid"]
+            d.pen_length, d.tar_length = cfg["pen_length"], cfg["tar_length"]
+            for i in range(3):
+                d.target_axis[i] = float(cfg["target_axis"][i])
+            d.w_pos_align, d.w_rot_align, d.w_r_act_reg, d.w_drop, d.w_r_bonus = cfg["reorient_weights"]
         if cfg.get("kind") == "walk":
             d.kind = 1
             d.foot_l_bid, d.foot_r_bid, d.pelvis_bid, d.torso_bid = cfg["foot_l"], cfg["foot_r"], cfg["pelvis"], cfg["torso"]

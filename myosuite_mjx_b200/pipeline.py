@@ -156,3 +156,25 @@ class WalkEnv(PipelineEnv):
         self.env.step(action)
         state.metrics.update(**self._metrics())
         return state.replace(pipeline_state=self._data, obs=self.env.obs, reward=self.env.reward[:, 0], done=self.env.done[:, 0])
+
+
+class ReorientEnv(WalkEnv):
+    """myoHandReorient (reference: myosuite/envs/myo/myobase/reorient_sar_v0.py ProprioceptiveEnvV0 with the per-episode
+    target orientation of Geometries8EnvV0.reset) in the reset(rng) / step(State, action) shape.  The per-episode change of
+    the object's shape is not reproduced (envs.reorient_config)."""
+
+    def __init__(self, sys, n_frames=5, nworld=1, fields=None, **kw):
+        from . import envs
+        base_kw = {k: kw.pop(k) for k in ("device", "nconmax", "njmax", "backend") if k in kw}
+        if not isinstance(sys, mjx.Model):
+            sys = envs.apply_reorient_setup(sys)
+        if fields is None:
+            fields = mjx.CORE_FIELDS + envs.REORIENT_FIELDS
+        PipelineEnv.__init__(self, sys, n_frames=n_frames, nworld=nworld, fields=fields, **base_kw)
+        self.cfg = envs.reorient_config(self.sys.mj, frame_skip=n_frames, **kw)
+        self.env = envs.FusedEnv(self._data, self.cfg)
+
+    def _metrics(self):
+        terms = self.env.rwd_terms
+        from .envs import REORIENT_RWD_TERMS
+        return {k: terms[:, i] for i, k in enumerate(REORIENT_RWD_TERMS)}

@@ -33,6 +33,8 @@ SPECS = {
                                                             normalize_act=True, pose_thd=0.7, reset_type="random", target_type="generate")),
     "myoLegWalk-v0": ("legs", "walk", 1000, dict(normalize_act=True, min_height=0.8, max_rot=0.8, hip_period=100, reset_type="init", target_x_vel=0.0,
                                                  target_y_vel=1.2, target_rot=None)),
+    # Geometries8EnvV0: target orientation per episode as registered; the object's per-episode shape change is not reproduced
+    "myoHandReorient8-v0": ("hand_sar", "reorient", 50, dict(normalize_act=True, n_frames=5)),
 }
 for _k in range(10):   # ASL evaluation envs, one per numeral (__init__.py:383-396)
     SPECS["myoHandPose%dFixed-v0" % _k] = ("hand_pose", "pose", 100, dict(target_jnt_value=ASL_QPOS[_k], normalize_act=True, pose_thd=0.7, reset_type="init",
@@ -67,5 +69,5 @@ def make(env_id, nworld=1, model=None, **overrides):
         kw.setdefault("target_type", "generate" if "target_jnt_range" in kw else "fixed")
     kw.update(horizon=horizon)
     kw.update(overrides)
-    cls = pipeline.PoseEnv if kind == "pose" else pipeline.WalkEnv
+    cls = {"pose": pipeline.PoseEnv, "walk": pipeline.WalkEnv, "reorient": pipeline.ReorientEnv}[kind]
     return cls(model, nworld=nworld, **kw)

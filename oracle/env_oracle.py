@@ -194,3 +194,43 @@ def walk_obs_reward(c, qpos, qvel, act, cvel, xipos, xpos, xquat, alen, avel, af
          "sparse": vel_reward, "solved": vel_reward >= 1.0, "done": done}
     r["dense"] = w[0] * vel_reward + w[1] * done + w[2] * cyclic + w[3] * ref_rot + w[4] * joint_angle
     return od, r
+
+
+# ---------------------------------------------------------------------------------------------------- reorient env
+def euler2quat(euler):
+    """myosuite/utils/quat_math.py:77-93."""
+    euler = np.asarray(euler, float)
+    ai, aj, ak = euler[..., 2] / 2, -euler[..., 1] / 2, euler[..., 0] / 2
+    si, sj, sk, ci, cj, ck = np.sin(ai), np.sin(aj), np.sin(ak), np.cos(ai), np.cos(aj), np.cos(ak)
+    cc, cs, sc, ss = ci * ck, ci * sk, si * ck, si * sk
+    return np.stack([cj * cc + sj * ss, cj * cs - sj * sc, -(cj * ss + sj * cc), cj * sc - sj * cs], axis=-1)
+
+
+def reorient_des_rot(c, seed, gworld, episode):
+    """obj_des_rot of a freshly reset world: reorient_sar_v0.py:251-257 with the library's counter-based draws."""
+    if c["target_type"] != "generate":
+        return np.asarray(c["target_value"], float)
+    e0 = np.float32(-1.0) + np.float32(2.0) * uniform(seed, gworld, episode, 0, 0)
+    e1 = np.float32(-0.8) + np.float32(2.0) * uniform(seed, gworld, episode, 0, 1)
+    w, x, y, z = euler2quat(np.array([e0, e1, 0.0], float))
+    R = np.array([[1 - 2 * (y * y + z * z), 2 * (x * y - w * z), 2 * (x * z + w * y)], [2 * (x * y + w * z), 1 - 2 * (x * x + z * z), 2 * (y * z - w * x)],
+                  [2 * (x * z - w * y), 2 * (y * z + w * x), 1 - 2 * (x * x + y * y)]])
+    return R @ np.asarray(c["target_axis"], float) / c["tar_length"]
+
+
+def reorient_obs_reward(c, qpos, qvel, act, obj_pos, eps_pos, top_pos, bot_pos, des_rot, alen, avel, afrc):
+    """reorient_sar_v0.py:115-173, batched over the leading axis.  `des_rot` is (geom_xpos[t_top] - geom_xpos[t_bot]) / tar_length."""
+    obj_rot = (top_pos - bot_pos) / c["pen_length"]
+    od = {"hand_jnt": qpos[..., :-6], "obj_pos": obj_pos, "obj_vel": qvel[..., -6:] * c["dt"], "obj_rot": obj_rot, "obj_des_rot": des_rot,
+          "obj_err_pos": obj_pos - eps_pos, "obj_err_rot": obj_rot - des_rot, "act": act, "mlen": alen, "mvel": avel, "mforce": afrc}
+    pos_align = np.linalg.norm(od["obj_err_pos"], axis=-1)
+    rot_align = np.sum(obj_rot * des_rot, axis=-1) / (np.linalg.norm(obj_rot, axis=-1) * np.linalg.norm(des_rot, axis=-1))
+    dropped = pos_align > 0.075
+    na = act.shape[-1]
+    act_mag = np.linalg.norm(act, axis=-1) / na if na else 0
+    w = c["reorient_weights"]
+    r = {"pos_align": -1.0 * pos_align, "rot_align": rot_align, "act_reg": -1.0 * act_mag, "drop": -1.0 * dropped,
+         "bonus": 1.0 * (rot_align > 0.9) * (pos_align < 0.075) + 5.0 * (rot_align > 0.95) * (pos_align < 0.075),
+         "sparse": -1.0 * pos_align + rot_align, "solved": (rot_align > 0.95) & (~dropped), "done": dropped}
+    r["dense"] = w[0] * r["pos_align"] + w[1] * r["rot_align"] + w[2] * r["act_reg"] + w[3] * r["drop"] + w[4] * r["bonus"]
+    return od, r

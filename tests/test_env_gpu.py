@@ -287,6 +287,80 @@ def test_walk_env_step_semantics(models):
     assert saw_reset and torch.isfinite(st.obs).all() and torch.isfinite(st.reward).all()
 
 
+def test_reorient_forward_matches_reference_golden(models):
+    """Reorient obs / reward terms / done of given mjData fields against the reference's own ProprioceptiveEnvV0 code
+    (tests/golden/make_reorient_kat.py).  float32: obs 2e-6 relative per key, reward terms 1e-5 (rot_align is a ratio of
+    float32 sums), thresholded terms exact away from the 0.075 / 0.9 / 0.95 thresholds."""
+    import torch
+    from myosuite_mjx_b200 import envs, pipeline
+    R = np.load(os.path.join(os.path.dirname(__file__), "golden", "reorient_kat.npz"))
+    m = models("hand_sar")
+    n = R["qpos"].shape[0]
+    env = pipeline.ReorientEnv(m, nworld=n, auto_reset=False, horizon=0, randomize_target=False)
+    env.reset(0)
+    d, e, c = env._data, env.env, env.cfg
+    dev = d.qpos.device
+    T = lambda a: torch.as_tensor(np.asarray(a, dtype=np.float32), device=dev)
+    d.qpos.copy_(T(R["qpos"])); d.qvel.copy_(T(R["qvel"])); d.act.copy_(T(R["act"]))
+    d.actuator_length.copy_(T(R["actuator_length"])); d.actuator_velocity.copy_(T(R["actuator_velocity"])); d.actuator_force.copy_(T(R["actuator_force"]))
+    d.xpos[:, c["obj_bid"]] = T(R["xpos"][:, 0]); d.site_xpos[:, c["eps_ball_sid"]] = T(R["site_xpos"][:, 0])
+    d.geom_xpos[:, c["top_gid"]] = T(R["geom_xpos"][:, 0]); d.geom_xpos[:, c["bot_gid"]] = T(R["geom_xpos"][:, 1])
+    e.target.copy_(T((R["geom_xpos"][:, 2].astype(np.float64) - R["geom_xpos"][:, 3]) / c["tar_length"]))
+    e.forward()
+    obs = e.obs.cpu().numpy()
+    o = 0
+    for k in c["obs_keys"]:
+        ref = R["obs_" + k]
+        got = obs[:, o:o + ref.shape[1]]; o += ref.shape[1]
+        assert np.abs(got - ref).max() <= 2e-6 * max(1.0, np.abs(ref).max()), k
+    assert o == obs.shape[1]
+    terms = e.rwd_terms.cpu().numpy()
+    pos, rot = -R["rwd_pos_align"], R["rwd_rot_align"]
+    safe = (np.abs(pos - 0.075) > 1e-5) & (np.abs(rot - 0.9) > 1e-5) & (np.abs(rot - 0.95) > 1e-5)
+    assert safe.sum() > 0.95 * n
+    for i, k in enumerate(envs.REORIENT_RWD_TERMS):
+        g = R["rwd_" + k].astype(np.float64)
+        sel = safe if k in ("drop", "bonus", "solved", "done") else slice(None)
+        assert np.abs(terms[:, i][sel] - g[sel]).max() <= 1e-5 * max(1.0, np.abs(g).max()), k
+    assert np.abs(e.reward.cpu().numpy()[:, 0][safe] - R["rwd_dense"][safe]).max() < 2e-4
+
+
+def test_reorient_env_step_semantics(models):
+    """myoHandReorient8-v0 through the registry: desired orientations per episode equal the oracle's (shared counter-based
+    draws + the reference's euler2quat), the observation equals the oracle's reorient_obs_reward of the bound fields (which
+    describe the stepped state), dropped worlds restart from the open-hand pose with a new target."""
+    import env_oracle as eo
+    import torch
+    from myosuite_mjx_b200 import registry
+    m = models("hand_sar")
+    nw = 16
+    env = registry.make("myoHandReorient8-v0", nworld=nw, model=m, horizon=6, seed=0)
+    st = env.reset(21)
+    d, e, c = env._data, env.env, env.cfg
+    assert c["frame_skip"] == 5 and c["dt"] == pytest.approx(0.01)
+    want = np.stack([eo.reorient_des_rot(c, 21, w, 0) for w in range(nw)])
+    assert np.abs(e.target.cpu().numpy() - want).max() < 2e-6 and np.abs(np.linalg.norm(want, axis=1) - 1).max() < 1e-6
+    assert np.array_equal(d.qpos.cpu().numpy(), np.tile(c["init_qpos"], (nw, 1)))
+    g = torch.Generator(device="cuda"); g.manual_seed(9)
+    nreset = 0
+    for t in range(8):
+        st = env.step(st, torch.rand((nw, m.nu), generator=g, device="cuda") * 2 - 1)
+        f = lambda name: getattr(d, name).cpu().numpy().astype(np.float64)
+        xp, sx, gx = f("xpos").reshape(nw, -1, 3), f("site_xpos").reshape(nw, -1, 3), f("geom_xpos").reshape(nw, -1, 3)
+        od, r = eo.reorient_obs_reward(c, f("qpos"), f("qvel"), f("act"), xp[:, c["obj_bid"]], sx[:, c["eps_ball_sid"]], gx[:, c["top_gid"]], gx[:, c["bot_gid"]],
+                                       e.target.cpu().numpy().astype(np.float64), f("actuator_length"), f("actuator_velocity"), f("actuator_force"))
+        ref = np.concatenate([od[k] for k in c["obs_keys"]], axis=-1)
+        assert np.abs(st.obs.cpu().numpy() - ref).max() < 1e-4 * max(1.0, np.abs(ref).max()), t
+        ended = st.done.cpu().numpy() > 0
+        if ended.any():
+            nreset += int(ended.sum())
+            assert np.array_equal(d.qpos.cpu().numpy()[ended], np.tile(c["init_qpos"], (int(ended.sum()), 1)))
+            ep = e.episode.cpu().numpy()[:, 0]
+            want = np.stack([eo.reorient_des_rot(c, 21, w, ep[w] - 1) for w in np.nonzero(ended)[0]])
+            assert np.abs(e.target.cpu().numpy()[ended] - want).max() < 2e-6
+    assert nreset >= nw and torch.isfinite(st.obs).all() and torch.isfinite(st.reward).all()
+
+
 def test_registry_pose_envs(models):
     """The registered kwargs of the BASELINE pose configs (myobase/__init__.py) reach the device env."""
     import torch

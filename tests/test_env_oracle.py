@@ -105,3 +105,25 @@ def test_walk_obs_and_reward_match_reference(models):
     np.testing.assert_array_equal(r["done"], W["rwd_done"] > 0)
     np.testing.assert_array_equal(r["solved"], W["rwd_solved"] > 0)
     assert 0.2 < r["done"].mean() < 0.8
+
+
+def test_reorient_obs_and_reward_match_reference(models):
+    """oracle/env_oracle.reorient_obs_reward and euler2quat against vectors produced by the reference's own
+    ProprioceptiveEnvV0.get_obs_dict / get_reward_dict and quat_math.euler2quat (tests/golden/make_reorient_kat.py)."""
+    from myosuite_mjx_b200 import envs
+    R = np.load(os.path.join(os.path.dirname(__file__), "golden", "reorient_kat.npz"))
+    c = envs.reorient_config(models("hand_sar"))
+    assert c["pen_length"] == pytest.approx(0.07) and c["tar_length"] == pytest.approx(0.07)
+    assert sorted(c["obs_keys"]) == sorted(R["default_obs_keys"]) and tuple(c["reorient_weights"]) == tuple(R["weights"])
+    f = lambda k: R[k].astype(np.float64)
+    g = f("geom_xpos")
+    od, r = eo.reorient_obs_reward(c, f("qpos"), f("qvel"), f("act"), f("xpos")[:, 0], f("site_xpos")[:, 0], g[:, 0], g[:, 1], (g[:, 2] - g[:, 3]) / c["tar_length"],
+                                   f("actuator_length"), f("actuator_velocity"), f("actuator_force"))
+    for k in od:
+        np.testing.assert_allclose(od[k], R["obs_" + k], rtol=1e-12, atol=1e-12, err_msg=k)
+    for k in ("pos_align", "rot_align", "act_reg", "drop", "bonus", "sparse", "dense"):
+        np.testing.assert_allclose(r[k], R["rwd_" + k], rtol=1e-12, atol=1e-12, err_msg=k)
+    np.testing.assert_array_equal(r["done"], R["rwd_done"] > 0)
+    np.testing.assert_array_equal(r["solved"], R["rwd_solved"] > 0)
+    assert 0.2 < r["done"].mean() < 0.8 and (r["bonus"] == 1).sum() > 3 and (r["bonus"] == 6).sum() > 3
+    np.testing.assert_allclose(eo.euler2quat(R["euler"]), R["euler_quat"], rtol=0, atol=1e-15)
