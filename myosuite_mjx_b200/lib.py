@@ -64,6 +64,12 @@ def lib():
     return _lib
 
 
+def has_xla_ffi():
+    """True when the library was built with the jax.ffi targets (csrc/xla_ffi.cc; needs jaxlib's XLA FFI headers,
+    `make XLA_INC=...`).  This image has no jax, so the default build exports neither MyoStep nor MyoForward."""
+    return hasattr(lib(), "MyoStep") and hasattr(lib(), "MyoForward")
+
+
 def check(rc):
     if rc != 0:
         raise MyoError(f"libmyostep error {rc}: {lib().myo_last_error().decode()}")
