@@ -8,7 +8,6 @@
 //   qM                                                                          (mj_crb, dense symmetric)
 //   efc_J                                                                       (mj_makeConstraint, dense rows)
 //   contact_* , efc_pos/margin/D/aref/force/type, xanchor, xaxis, cdof          (small per-row copies)
-//   cinert, crb, subtree_com                                                    (mj_comPos / mj_crb: sums over a body's subtree)
 // Same arithmetic, in the same order, as the step kernel's own writers for these fields (which remain in team.cu and
 // run when this kernel is switched off with MYO_WIDE_OUT=0).
 #include <cuda_runtime.h>
@@ -260,95 +259,17 @@ __global__ void __launch_bounds__(OUT_THREADS, OUT_MINBLOCKS) outKernel(int slot
     }
   }
 }
-// cinert, crb, subtree_com (mj_comPos / mj_crb outputs): sums over a body's depth-first subtree [b, body_subend[b]).  A
-// kernel of its own, one thread per (world, body): its live state (two 10-vectors, three 3x3 products) does not fit the
-// 40 registers that keep 12 CTAs of outKernel resident.  Same arithmetic and summation order as the step kernel's writer.
-template <int STRIDE>
-__global__ void __launch_bounds__(128, 6) outInertialKernel(int slot, int nworld, const int* __restrict__ mask, const float* __restrict__ scratch) {
-  const DevModel& D = oP[slot].D; const SmemLayout& L = oP[slot].L; const FieldPtrs& F = oP[slot].F;
-  CtxT<STRIDE> c; c.w = (size_t)blockIdx.x * 128 + threadIdx.x; c.nw = (size_t)nworld;
-  if (c.w >= c.nw) return;
-  if (mask && !mask[c.w]) return;
-  c.sm = scratch + (c.w / STRIDE) * (size_t)L.total * STRIDE + (c.w % STRIDE);
-  void* cin = F.p[MYO_F_CINERT]; void* crbo = F.p[MYO_F_CRB]; void* scom = F.p[MYO_F_SUBTREE_COM];
-  for (int b = blockIdx.y; b < D.nbody; b += gridDim.y) {
-    const size_t nw = c.nw, w = c.w;
-    const int e = (crbo || scom) ? D.body_subend[b] : b + 1;
-    float mx[3] = {0.f, 0.f, 0.f}, own[3] = {0.f, 0.f, 0.f}, acc[10];
-#pragma unroll
-    for (int k = 0; k < 10; k++) acc[k] = 0.f;
-#pragma unroll 1
-    for (int q = b; q < e; q++) {
-      float p[3], M[9], R[9], ip[3];
-      framePose(c, L, D.body_frame[q], D.body_off_pos + 3 * q, D.body_off_mat + 9 * q, p, M, R);
-      const float* il = D.body_ipos + 3 * q;
-      const float m = D.body_mass[q];
-#pragma unroll
-      for (int i = 0; i < 3; i++) {
-        ip[i] = p[i] + fmaf(M[3 * i], il[0], fmaf(M[3 * i + 1], il[1], M[3 * i + 2] * il[2]));
-        mx[i] += __fmul_rn(m, ip[i]);   // the step kernel adds the rounded products (tmpbody)
-      }
-      if (q == b) { own[0] = ip[0]; own[1] = ip[1]; own[2] = ip[2]; }
-      if (cin || crbo) {
-        float cc[10];
-        if (q == 0) {
-#pragma unroll
-          for (int k = 0; k < 10; k++) cc[k] = 0.f;
-        } else {
-          const float* im = D.body_imat + 9 * q;
-          float IM[9];
-#pragma unroll
-          for (int i = 0; i < 3; i++)
-#pragma unroll
-            for (int j = 0; j < 3; j++) IM[3 * i + j] = fmaf(M[3 * i], im[j], fmaf(M[3 * i + 1], im[3 + j], M[3 * i + 2] * im[6 + j]));
-          const float i0 = D.body_inertia[3 * q], i1 = D.body_inertia[3 * q + 1], i2 = D.body_inertia[3 * q + 2];
-          const int rc = L.rootcom + 3 * D.body_root[q];
-          const float ox = ip[0] - S(c, rc), oy = ip[1] - S(c, rc + 1), oz = ip[2] - S(c, rc + 2);
-          cc[0] = IM[0] * IM[0] * i0 + IM[1] * IM[1] * i1 + IM[2] * IM[2] * i2 + m * (oy * oy + oz * oz);
-          cc[1] = IM[3] * IM[3] * i0 + IM[4] * IM[4] * i1 + IM[5] * IM[5] * i2 + m * (ox * ox + oz * oz);
-          cc[2] = IM[6] * IM[6] * i0 + IM[7] * IM[7] * i1 + IM[8] * IM[8] * i2 + m * (ox * ox + oy * oy);
-          cc[3] = IM[0] * IM[3] * i0 + IM[1] * IM[4] * i1 + IM[2] * IM[5] * i2 - m * ox * oy;
-          cc[4] = IM[0] * IM[6] * i0 + IM[1] * IM[7] * i1 + IM[2] * IM[8] * i2 - m * ox * oz;
-          cc[5] = IM[3] * IM[6] * i0 + IM[4] * IM[7] * i1 + IM[5] * IM[8] * i2 - m * oy * oz;
-          cc[6] = m * ox; cc[7] = m * oy; cc[8] = m * oz; cc[9] = m;
-        }
-        if (q == b && cin) {
-          Row o(cin, 10 * (size_t)b, nw, w);
-#pragma unroll
-          for (int k = 0; k < 10; k++) o.put(cc[k]);
-        }
-        if (b > 0)
-#pragma unroll
-          for (int k = 0; k < 10; k++) acc[k] += cc[k];
-      }
-    }
-    if (scom) {
-      const float Ms = D.body_subtreemass[b];
-      Row o(scom, 3 * (size_t)b, nw, w);
-      if (Ms < 1e-15f) { o.put(own[0]); o.put(own[1]); o.put(own[2]); }   // MuJoCo: massless subtree -> xipos
-      else { const float s = 1.f / Ms; o.put(mx[0] * s); o.put(mx[1] * s); o.put(mx[2] * s); }
-    }
-    if (crbo) {
-      Row o(crbo, 10 * (size_t)b, nw, w);
-#pragma unroll
-      for (int k = 0; k < 10; k++) o.put(acc[k]);
-    }
-
-  }
-}
-
 }  // namespace
 
-// fields these kernels write (the step kernel is given null pointers for them when the wide path is on)
+// fields this kernel writes (the step kernel is given null pointers for them when the wide path is on)
 const int kWideOutFields[] = {MYO_F_SITE_XPOS, MYO_F_SITE_XMAT, MYO_F_GEOM_XPOS, MYO_F_GEOM_XMAT, MYO_F_XPOS, MYO_F_XQUAT, MYO_F_XMAT,
                               MYO_F_XIPOS, MYO_F_XIMAT, MYO_F_TEN_J, MYO_F_ACTUATOR_MOMENT, MYO_F_QM, MYO_F_EFC_J,
                               MYO_F_CONTACT_GEOM, MYO_F_CONTACT_DIM, MYO_F_CONTACT_EFC_ADDRESS, MYO_F_CONTACT_DIST, MYO_F_CONTACT_POS,
                               MYO_F_CONTACT_FRAME, MYO_F_CONTACT_INCLUDEMARGIN, MYO_F_CONTACT_FRICTION, MYO_F_CONTACT_SOLREF,
                               MYO_F_CONTACT_SOLIMP, MYO_F_EFC_POS, MYO_F_EFC_MARGIN, MYO_F_EFC_D, MYO_F_EFC_AREF, MYO_F_EFC_FORCE,
-                              MYO_F_EFC_TYPE, MYO_F_XANCHOR, MYO_F_XAXIS, MYO_F_CDOF, MYO_F_CINERT, MYO_F_CRB, MYO_F_SUBTREE_COM};
+                              MYO_F_EFC_TYPE, MYO_F_XANCHOR, MYO_F_XAXIS, MYO_F_CDOF};
 const int kNumWideOutFields = sizeof(kWideOutFields) / sizeof(int);
 
-static bool g_inertial[MYO_PARAM_SLOTS];   // cinert / crb / subtree_com bound: the second kernel runs
 int myo_out_upload(int slot, const DevModel& D, const SmemLayout& L, const FieldPtrs& F, void* stream) {
   static OutParams staging[MYO_PARAM_SLOTS];   // must outlive the async copy
   if (slot < 0 || slot >= MYO_PARAM_SLOTS) return -1;
@@ -356,7 +277,6 @@ int myo_out_upload(int slot, const DevModel& D, const SmemLayout& L, const Field
   P.D = D; P.L = L;
   for (int f = 0; f < MYO_F_COUNT; f++) P.F.p[f] = nullptr;
   for (int i = 0; i < kNumWideOutFields; i++) P.F.p[kWideOutFields[i]] = F.p[kWideOutFields[i]];
-  g_inertial[slot] = P.F.p[MYO_F_CINERT] || P.F.p[MYO_F_CRB] || P.F.p[MYO_F_SUBTREE_COM];
   return cudaMemcpyToSymbolAsync(oP, &P, sizeof(OutParams), (size_t)slot * sizeof(OutParams), cudaMemcpyHostToDevice, (cudaStream_t)stream) == cudaSuccess ? 0 : -1;
 }
 int myo_out_launch(int slot, int nworld, int stride, const int* mask, int posvel, const float* scratch, void* stream) {
@@ -375,19 +295,6 @@ int myo_out_launch(int slot, int nworld, int stride, const int* mask, int posvel
     case 4: outKernel<4><<<grid, OUT_THREADS, 0, st>>>(slot, nworld, mask, posvel, scratch); break;
     case 2: outKernel<2><<<grid, OUT_THREADS, 0, st>>>(slot, nworld, mask, posvel, scratch); break;
     default: return -1;
-  }
-  if (g_inertial[slot]) {
-    dim3 gi(grid.x, 1);
-    gi.y = (unsigned)((148 * 6 * 4 + gi.x - 1) / gi.x);   // ~4 waves of short CTAs; bodies are strided over grid.y
-    if (gi.y < 1) gi.y = 1;
-    switch (stride) {
-      case 32: outInertialKernel<32><<<gi, 128, 0, st>>>(slot, nworld, mask, scratch); break;
-      case 16: outInertialKernel<16><<<gi, 128, 0, st>>>(slot, nworld, mask, scratch); break;
-      case 8: outInertialKernel<8><<<gi, 128, 0, st>>>(slot, nworld, mask, scratch); break;
-      case 4: outInertialKernel<4><<<gi, 128, 0, st>>>(slot, nworld, mask, scratch); break;
-      case 2: outInertialKernel<2><<<gi, 128, 0, st>>>(slot, nworld, mask, scratch); break;
-    }
-    myo_count_launch(1);
   }
   return cudaPeekAtLastError() == cudaSuccess ? 0 : -1;
 }
