@@ -265,7 +265,7 @@ def main():
             "data": "synthetic",
             "config": {"workload": WORKLOAD.format(model=args.model, nworld=nw), "nworld_per_gpu": nw, "fields": args.fields,
                        "nsub_per_launch": args.nsub, "frame_skip_ctrl_hold": FRAME_SKIP, "nconmax": d.nconmax, "njmax": d.njmax,
-                       "scratch_bytes_per_world": d.smem_bytes, "bytes_per_world_step": bytes_per_world,
+                       "scratch_bytes_per_world": d.smem_bytes, "lanes_per_world": d.team, "step_ctas_per_sm": d.ctas_per_sm, "bytes_per_world_step": bytes_per_world,
                        "l2": "working set per step (%.0f MB) exceeds the 126 MB L2" % (bytes_per_world * nw / 1e6),
                        "partition": "worlds by index, no collective on the step path",
                        "worlds_with_status_flags": int(stats[0].item())},

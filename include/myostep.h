@@ -192,7 +192,8 @@ void myo_batch_destroy(myo_batch *b);
 int myo_batch_nconmax(const myo_batch *b);
 int myo_batch_njmax(const myo_batch *b);
 int myo_batch_smem_bytes(const myo_batch *b);
-int myo_batch_team(const myo_batch *b);         /* lanes per world of the kernel variant picked for this batch size (1..16) */   /* bytes of per-world scratch (L1-cached local memory of the world's thread) */
+int myo_batch_team(const myo_batch *b);         /* lanes per world of the kernel variant picked for this batch size (1..16) */
+int myo_batch_ctas_per_sm(const myo_batch *b);  /* co-resident step-kernel CTAs per SM of that variant (2 above 8288 worlds) */
 
 /* Per-world element count / element size of a field for this batch (0 elements = field absent for the model). */
 int64_t myo_field_count(const myo_batch *b, int field);

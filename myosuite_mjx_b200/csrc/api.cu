@@ -14,17 +14,26 @@
 
 namespace {
 const TeamVariant kVariants[] = {
-    {1, myo_team_upload_1, myo_team_launch_1, myo_team_scratch_1}, {2, myo_team_upload_2, myo_team_launch_2, myo_team_scratch_2},
-    {4, myo_team_upload_4, myo_team_launch_4, myo_team_scratch_4}, {8, myo_team_upload_8, myo_team_launch_8, myo_team_scratch_8},
-    {16, myo_team_upload_16, myo_team_launch_16, myo_team_scratch_16}};
+    {1, 1, myo_team_upload_1, myo_team_launch_1, myo_team_scratch_1}, {2, 1, myo_team_upload_2, myo_team_launch_2, myo_team_scratch_2},
+    {4, 1, myo_team_upload_4, myo_team_launch_4, myo_team_scratch_4}, {8, 1, myo_team_upload_8, myo_team_launch_8, myo_team_scratch_8},
+    {16, 1, myo_team_upload_16, myo_team_launch_16, myo_team_scratch_16},
+    {8, 2, myo_team_upload_8x2, myo_team_launch_8x2, myo_team_scratch_8x2}};
 int64_t g_launches = 0;
-// lanes per world: the step is latency-bound, so small batches get wider teams (more warps per SM)
+// lanes per world: the step is latency-bound, so small batches get wider teams (more warps per SM).  Up to 8288 worlds:
+// the widest team whose warps are all resident at once in one 14-warp CTA per SM (148 SMs, <= 128 registers).  Above
+// that: 8 lanes per world with TWO co-resident CTAs per SM (<= 72 registers): the second CTA fills the first one's phase
+// barriers and load stalls (profiles/r1v_nworld_sweep.txt: 16384 worlds 2.03 ms/step against 2.28 for two waves of the
+// one-CTA build and 2.63 for 4 lanes per world).
 const TeamVariant* pickVariant(int nworld) {
-  int team = 16;   // widest team whose warps are all resident at once (one 14-warp CTA per SM, 148 SMs)
-  while (team > 1 && (int64_t)nworld * team > (int64_t)148 * 14 * 32) team >>= 1;
-  if (const char* e = getenv("MYO_TEAM")) team = atoi(e);
+  const int64_t resident = (int64_t)148 * 14 * 32;
+  int team = 16, ctas = 1;
+  while (team > 8 && (int64_t)nworld * team > resident) team >>= 1;
+  if ((int64_t)nworld * team > resident) ctas = 2;
+  if (const char* e = getenv("MYO_TEAM")) { team = atoi(e); ctas = 1; }   // developer knobs
+  if (const char* e = getenv("MYO_CTAS")) ctas = atoi(e);
+  for (const TeamVariant& v : kVariants) if (v.team == team && v.ctas_per_sm == ctas) return &v;
   for (const TeamVariant& v : kVariants) if (v.team == team) return &v;
-  return &kVariants[2];
+  return &kVariants[3];
 }
 thread_local std::string g_err;
 bool g_slot_used[64] = {false};
@@ -75,7 +84,9 @@ int64_t fieldCount(const DevModel& D, int f) {
     case MYO_F_CVEL: return 6 * nb;
     case MYO_F_TEN_LENGTH: case MYO_F_TEN_VELOCITY: return D.nten;
     case MYO_F_TEN_J: return (int64_t)D.nten * nv;
-    case MYO_F_TEN_WRAPADR: case MYO_F_TEN_WRAPNUM: case MYO_F_WRAP_OBJ: case MYO_F_WRAP_XPOS: return 0;  // render-only path points: not materialised
+    case MYO_F_TEN_WRAPADR: case MYO_F_TEN_WRAPNUM: return D.nten;
+    case MYO_F_WRAP_OBJ: return 2 * (int64_t)D.nwrap;     // one entry per path point (mjData: [nwrap, 2])
+    case MYO_F_WRAP_XPOS: return 6 * (int64_t)D.nwrap;    // three per path point (mjData: [nwrap, 6])
     case MYO_F_ACTUATOR_MOMENT: return (int64_t)D.nu * nv;
     case MYO_F_QM: case MYO_F_QLD: return nv * nv;
     case MYO_F_CONTACT_GEOM: case MYO_F_CONTACT_SOLREF: return 2 * nc;
@@ -171,6 +182,7 @@ int myo_batch_nconmax(const myo_batch* b) { return b ? b->D.nconmax : 0; }
 int myo_batch_njmax(const myo_batch* b) { return b ? b->D.njmax : 0; }
 int myo_batch_smem_bytes(const myo_batch* b) { return b ? b->L.total * 4 : 0; }
 int myo_batch_team(const myo_batch* b) { return b ? b->kern->team : 0; }
+int myo_batch_ctas_per_sm(const myo_batch* b) { return b ? b->kern->ctas_per_sm : 0; }
 int64_t myo_field_count(const myo_batch* b, int field) { return (b && field >= 0 && field < MYO_F_COUNT) ? fieldCount(b->D, field) : 0; }
 
 int myo_batch_bind(myo_batch* b, int field, void* dev_ptr, int64_t nbytes) {
@@ -201,6 +213,16 @@ static int launch(myo_batch* b, int nsub, int forward_only, const int32_t* mask,
         if (b->F.p[kWideOutFields[i]]) { Fstep.p[kWideOutFields[i]] = nullptr; b->wide = true; }
     if (b->kern->upload(b->slot, b->D, b->L, Fstep, stream) != 0) return fail(MYO_ERR_CUDA, "parameter upload failed");
     if (b->wide && myo_out_upload(b->slot, b->D, b->L, b->F, stream) != 0) return fail(MYO_ERR_CUDA, "parameter upload failed");
+    // Path-point buffers: the kernel clears only the entries a wrap state can reach; the rest of a newly bound buffer is
+    // zeroed here once (mj_makeData's zeros), on the caller's stream.
+    const int wf[2] = {MYO_F_WRAP_OBJ, MYO_F_WRAP_XPOS};
+    for (int i = 0; i < 2; i++) {
+      void* p = b->F.p[wf[i]];
+      if (!p || p == b->wrap_cleared[i]) continue;
+      if (cudaMemsetAsync(p, 0, (size_t)b->nworld * fieldCount(b->D, wf[i]) * 4, (cudaStream_t)stream) != cudaSuccess)
+        return fail(MYO_ERR_CUDA, "clearing the path-point buffers failed");
+      b->wrap_cleared[i] = p;
+    }
     b->dirty = false;
   }
   g_launches++;

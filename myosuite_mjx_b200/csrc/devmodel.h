@@ -67,6 +67,8 @@ struct DevModel {
   const float *body_off_mat, *body_imat, *geom_lmat, *site_lmat;   // 3x3 row-major rotations of the offsets above
   // ---- tendons
   const int *unit_tendon, *unit_type, *unit_s0, *unit_s1, *unit_geom, *unit_side, *unit_slot;
+  const int *unit_woff, *unit_gord, *unit_end, *gunit, *pul_off, *pul_gord, *ten_woff, *ten_gord;   // path-point outputs (plan.cu)
+  int ngunit, npulley;
   const int *unit_order;                       // [nunit] site-site units first, then the units that wrap a geom
   const float *unit_div, *unit_radius;
   const int *ten_ustart;                       // [nten+1]
@@ -117,7 +119,7 @@ struct SmemLayout {
       qacc, warm, tmpv, tforce;
   int counts;    // ncon, nefc, solver_niter of the last forward pass (int bits), read by the wide-output kernel
   // overlay region A (tendon stage)
-  int slots, ulen, uwrap, tmpbody;
+  int slots, ulen, uwrap, uwpt, gpre, tmpbody;
   // overlay region B (collision / constraint / solver stage)
   int cgpose, con, conJ, efc, H, nvec, limrow, basev, cand;
   int nv;        // copy of DevModel.nv (the launch sizes the shared-memory Hessian tiles from it)

@@ -16,6 +16,7 @@ void myo_make_layout(DevModel& D, int nconmax_req, int njmax_req, SmemLayout& L)
 // constant-memory parameter slots.
 struct TeamVariant {
   int team;
+  int ctas_per_sm;   // co-resident 14-warp CTAs per SM this build allows (1: <= 128 registers per thread, 2: <= 72)
   int (*upload)(int slot, const DevModel& D, const SmemLayout& L, const FieldPtrs& F, void* stream);
   // nsub substeps (forward_only: mj_forward; do_reset: mj_resetData + mj_forward on the masked worlds)
   int (*launch)(int slot, const SmemLayout& L, int nworld, int nsub, int forward_only, const int* reset_mask, int do_reset,
@@ -32,6 +33,7 @@ MYO_DECLARE_TEAM(2)
 MYO_DECLARE_TEAM(4)
 MYO_DECLARE_TEAM(8)
 MYO_DECLARE_TEAM(16)
+MYO_DECLARE_TEAM(8x2)
 struct myo_model {
   DevModel D;
   SmemLayout L;
@@ -48,6 +50,7 @@ struct myo_batch {
   const TeamVariant* kern;   // step kernel variant (lanes per world) chosen for this batch size
   bool dirty;    // parameters changed since the last upload
   bool wide;     // some wide output field is bound: the output kernel runs after the step kernel
+  void* wrap_cleared[2] = {nullptr, nullptr};   // wrap_obj / wrap_xpos buffers already zeroed once (api.cu launch)
   float* scratch; // per-world intermediates, [nwarps][L.total][worlds per warp]
   std::vector<void*> owned;
 };

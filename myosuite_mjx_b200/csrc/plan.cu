@@ -314,14 +314,20 @@ void myo_build_plan(const myo_model_desc& m, int nconmax_req, int njmax_req, Dev
   std::vector<Ent> ents;
   std::vector<int> u_t, u_type, u_s0, u_s1, u_g, u_side, u_slot, ten_ustart(m.ntendon + 1, 0);
   std::vector<float> u_div, u_rad;
+  // mjData path points (ten_wrapadr / ten_wrapnum / wrap_obj / wrap_xpos): a unit's first point sits at its STATIC offset
+  // (every unit unwrapped: one point per unit, one per branch end, one per pulley marker) plus two for every unit before
+  // it that currently wraps its geom.  *_gord = number of geom units before the item.
+  std::vector<int> u_woff, u_gord, u_end, gunit, pul_off, pul_gord, ten_woff(m.ntendon + 1, 0), ten_gord(m.ntendon + 1, 0);
+  int wstat = 0;
   int nslot = 0;
   for (int t = 0; t < m.ntendon; t++) {
     ten_ustart[t] = (int)u_t.size();
+    ten_woff[t] = wstat; ten_gord[t] = (int)gunit.size();
     int adr = m.tendon_adr[t], num = m.tendon_num[t], k = 0;
     double div = 1;
     while (k < num - 1) {
       int t0 = m.wrap_type[adr + k], t1 = m.wrap_type[adr + k + 1];
-      if (t0 == W_PULLEY) { div = m.wrap_prm[adr + k]; k++; continue; }
+      if (t0 == W_PULLEY) { div = m.wrap_prm[adr + k]; pul_off.push_back(wstat++); pul_gord.push_back((int)gunit.size()); k++; continue; }
       if (t1 == W_PULLEY) { k++; continue; }
       if (t0 != W_SITE) throw std::string("tendon path must alternate sites and wrap geoms");
       int u = (int)u_t.size(), s0 = m.wrap_objid[adr + k], s1, g = -1, side = -1, type = UNIT_SITE;
@@ -346,9 +352,19 @@ void myo_build_plan(const myo_model_desc& m, int nconmax_req, int njmax_req, Dev
       else { addseg(b0, b1, ENT_NOWRAP, 0); addseg(b0, bg, ENT_WRAP, 0); addseg(bg, b1, ENT_WRAP, 1); }
       u_t.push_back(t); u_type.push_back(type); u_s0.push_back(s0); u_s1.push_back(s1); u_g.push_back(g); u_side.push_back(side);
       u_slot.push_back(slot0); u_slot.push_back(slot1); u_div.push_back((float)div); u_rad.push_back(g >= 0 ? (float)m.geom_size[3 * g] : 0.f);
+      u_woff.push_back(wstat++); u_gord.push_back((int)gunit.size());
+      if (g >= 0) gunit.push_back(u);
+      const bool end = k == num - 1 || m.wrap_type[adr + k + 1] == W_PULLEY;   // last site of the tendon or of a pulley branch
+      u_end.push_back(end ? 1 : 0);
+      if (end) wstat++;
     }
   }
   ten_ustart[m.ntendon] = (int)u_t.size();
+  ten_woff[m.ntendon] = wstat; ten_gord[m.ntendon] = (int)gunit.size();
+  D.ngunit = (int)gunit.size(); D.npulley = (int)pul_off.size();
+  if (wstat + 2 * D.ngunit > 2 * m.nwrap) throw std::string("tendon path points exceed 2 * nwrap");
+  D.unit_woff = upload(u_woff, owned); D.unit_gord = upload(u_gord, owned); D.unit_end = upload(u_end, owned); D.gunit = upload(gunit, owned);
+  D.pul_off = upload(pul_off, owned); D.pul_gord = upload(pul_gord, owned); D.ten_woff = upload(ten_woff, owned); D.ten_gord = upload(ten_gord, owned);
   D.nunit = (int)u_t.size(); D.nslot = nslot; D.nentry = (int)ents.size();
   std::stable_sort(ents.begin(), ents.end(), [](const Ent& a, const Ent& b) { return a.tendon != b.tendon ? a.tendon < b.tendon : a.dof < b.dof; });
   std::vector<int> e_slot, e_dof, e_kind, e_unit, nz_estart, nz_t, nz_d, ten_nzstart(m.ntendon + 1, 0);
@@ -626,6 +642,7 @@ void myo_make_layout(DevModel& D, int nconmax_req, int njmax_req, SmemLayout& L)
   int base = o;
   // overlay A: tendon stage
   L.slots = take(6 * D.nslot); L.ulen = take(D.nunit); L.uwrap = take(D.nunit);
+  L.uwpt = take(6 * D.ngunit); L.gpre = take(D.ngunit + 1);   // tangent points / wrapped-unit prefix counts for the path-point outputs
   int endA = o;
   o = base;
   L.tmpbody = take(13 * D.nbody);   // position-output stage only (before the tendon stage)

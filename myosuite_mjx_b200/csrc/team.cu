@@ -581,6 +581,8 @@ __device__ __noinline__ float wrapGeom(f3 x0, f3 x1, f3 gpos, const float* gmat,
 // mj_tendon: path lengths + sparse moment arms
 __device__ __noinline__ void tendons(int slot, int fslot, SP sm, Tm t, World W) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L; const FieldPtrs& F = tP[fslot].F;
+  void* wx = F.p[MYO_F_WRAP_XPOS]; void* wo = F.p[MYO_F_WRAP_OBJ]; void* wa = F.p[MYO_F_TEN_WRAPADR]; void* wn = F.p[MYO_F_TEN_WRAPNUM];
+  const bool wantw = wx || wo || wa || wn;   // mjData path points requested
   TFOR(uo, D.nunit) {
     const int u = D.unit_order[uo];
     const int s0 = D.unit_s0[u], s1 = D.unit_s1[u], g = D.unit_geom[u];
@@ -595,6 +597,7 @@ __device__ __noinline__ void tendons(int slot, int fslot, SP sm, Tm t, World W) 
       f3 side = mk3(0.f, 0.f, 0.f);
       if (sid >= 0) { const int fs = D.site_frame[sid]; side = ld3(FR_POS(sm, L, fs)) + mulM(FR_MAT(sm, L, fs), ld3(D.site_lpos + 3 * sid)); }
       wlen = wrapGeom(p0, p1, gpos, gm, D.unit_radius[u], D.unit_type[u], sid >= 0, side, &w0, &w1);
+      if (wantw && wlen >= 0.f) { auto wp = sm + L.uwpt + 6 * D.unit_gord[u]; st3(wp, w0); st3(wp + 3, w1); }
     }
     const int sl0 = D.unit_slot[2 * u], sl1 = D.unit_slot[2 * u + 1];
     float len;
@@ -634,6 +637,43 @@ __device__ __noinline__ void tendons(int slot, int fslot, SP sm, Tm t, World W) 
     sm[L.tenlen + k] = acc;
   }
   TSYNC();
+  if (wantw) {
+    // Path points in mj_tendon's order: per unit its first site, the two tangent points if it wraps (wrap_obj = geom id),
+    // the last site at a tendon / pulley-branch end (wrap_obj -1), a marker per pulley (wrap_obj -2, position unset = 0).
+    // Offsets = static offsets + 2 x (wrapping units before the item); entries past the last point are zero.
+    const int ngu = D.ngunit;
+    if (t.tl == 0) {
+      int acc = 0;
+      for (int k = 0; k < ngu; k++) { sm[L.gpre + k] = __int_as_float(acc); acc += sm[L.uwrap + D.gunit[k]] != 0.f ? 1 : 0; }
+      sm[L.gpre + ngu] = __int_as_float(acc);
+    }
+    TSYNC();
+    auto put = [&](int i, f3 p, int obj) {
+      if (wx) { OUTF(wx, 3 * i) = p.x; OUTF(wx, 3 * i + 1) = p.y; OUTF(wx, 3 * i + 2) = p.z; }
+      if (wo) OUTI(wo, i) = obj;
+    };
+    TFOR(u, D.nunit) {
+      const int go = D.unit_gord[u], g = D.unit_geom[u];
+      const bool wrapped = sm[L.uwrap + u] != 0.f;
+      const int off = D.unit_woff[u] + 2 * __float_as_int(sm[L.gpre + go]);
+      const int s0 = D.unit_s0[u], f0 = D.site_frame[s0];
+      put(off, ld3(FR_POS(sm, L, f0)) + mulM(FR_MAT(sm, L, f0), ld3(D.site_lpos + 3 * s0)), -1);
+      if (wrapped) { auto wp = sm + L.uwpt + 6 * go; put(off + 1, ld3(wp), g); put(off + 2, ld3(wp + 3), g); }
+      if (D.unit_end[u]) {
+        const int s1 = D.unit_s1[u], f1 = D.site_frame[s1];
+        put(off + (wrapped ? 3 : 1), ld3(FR_POS(sm, L, f1)) + mulM(FR_MAT(sm, L, f1), ld3(D.site_lpos + 3 * s1)), -1);
+      }
+    }
+    TFOR(i, D.npulley) put(D.pul_off[i] + 2 * __float_as_int(sm[L.gpre + D.pul_gord[i]]), mk3(0.f, 0.f, 0.f), -2);
+    TFOR(k, D.nten) {
+      const int g0 = __float_as_int(sm[L.gpre + D.ten_gord[k]]), g1 = __float_as_int(sm[L.gpre + D.ten_gord[k + 1]]);
+      if (wa) OUTI(wa, k) = D.ten_woff[k] + 2 * g0;
+      if (wn) OUTI(wn, k) = D.ten_woff[k + 1] - D.ten_woff[k] + 2 * (g1 - g0);
+    }
+    // entries past the last point: only those a previous step can have written (all geom units wrapped); the rest of the
+    // buffer keeps the zeros it was given when it was bound (api.cu)
+    for (int i = D.ten_woff[D.nten] + 2 * __float_as_int(sm[L.gpre + ngu]) + t.tl; i < D.ten_woff[D.nten] + 2 * ngu; i += TEAM) put(i, mk3(0.f, 0.f, 0.f), 0);
+  }
   void* tl = F.p[MYO_F_TEN_LENGTH]; void* tj = F.p[MYO_F_TEN_J];
   if (tl) TFOR(k, D.nten) OUTF(tl, k) = sm[L.tenlen + k];
   if (tj) {
@@ -2081,7 +2121,10 @@ __global__ void quatKatKernel(int n, const float* __restrict__ qa, const float* 
 
 #define CAT2_(a, b) a##b
 #define CAT2(a, b) CAT2_(a, b)
-#define VFN(name) CAT2(name, TEAM)
+#ifndef VSUFFIX   // symbol suffix of this build of the kernel: the team width, or e.g. 8x2 for two co-resident CTAs per SM
+#define VSUFFIX TEAM
+#endif
+#define VFN(name) CAT2(name, VSUFFIX)
 
 int VFN(myo_team_upload_)(int slot, const DevModel& D, const SmemLayout& L, const FieldPtrs& F, void* stream) {
   static TParams staging[MYO_NSLOT];   // must outlive the async copy
@@ -2120,7 +2163,7 @@ size_t VFN(myo_team_scratch_)(const SmemLayout& L, int nworld) {
   const size_t nwarp = (size_t)(nworld + SCR_STRIDE - 1) / SCR_STRIDE;
   return (nwarp + CTA_WARPS - 1) / CTA_WARPS * CTA_WARPS * L.total * SCR_STRIDE;
 }
-#if TEAM == 1
+#if TEAM == 1 && CTA_MINBLOCKS == 1
 int myo_launch_quat_kat(int n, const float* qa, const float* qb, float* prod, float* mat, float* rotated, void* stream) {
   quatKatKernel<<<(n + 127) / 128, 128, 0, (cudaStream_t)stream>>>(n, qa, qb, prod, mat, rotated);
   return cudaPeekAtLastError() == cudaSuccess ? 0 : -1;

@@ -39,7 +39,7 @@ _SHAPES = {
     "crb": ("nbody", 10), "cdof": ("nv", 6), "cdof_dot": ("nv", 6), "cvel": ("nbody", 6), "ten_j": ("ntendon", "nv"),
     "actuator_moment": ("nu", "nv"), "qm": ("nv", "nv"), "qld": ("nv", "nv"), "contact_geom": (-1, 2), "contact_pos": (-1, 3),
     "contact_frame": (-1, 9), "contact_friction": (-1, 5), "contact_solref": (-1, 2), "contact_solimp": (-1, 5),
-    "efc_j": (-1, "nv"),
+    "efc_j": (-1, "nv"), "wrap_obj": (-1, 2), "wrap_xpos": (-1, 6),
 }
 
 
@@ -80,6 +80,7 @@ class Data:
         self.njmax = L.myo_batch_njmax(h)
         self.smem_bytes = L.myo_batch_smem_bytes(h)
         self.team = L.myo_batch_team(h)
+        self.ctas_per_sm = L.myo_batch_ctas_per_sm(h)
         self._t = {}
         dev = torch.device("cuda", model.device)
         if fields == "all":

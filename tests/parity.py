@@ -41,7 +41,8 @@ def oracle_forward(m, qpos, qvel, act, ctrl, fields, warm=None, use_float=False)
     import oracle
     o = oracle.Oracle(m, use_float=use_float)
     out = {k: [] for k in fields}
-    extra = {"ncon": [], "nefc": [], "contact_geom": [], "contact_dist": [], "contact_pos": [], "contact_frame": [], "niter": []}
+    extra = {"ncon": [], "nefc": [], "contact_geom": [], "contact_dist": [], "contact_pos": [], "contact_frame": [], "niter": [],
+             "ten_wrapadr": [], "ten_wrapnum": [], "wrap_obj": [], "wrap_xpos": []}
     for w in range(qpos.shape[0]):
         o.set_state(qpos[w], qvel[w], act[w], ctrl[w], warm[w] if warm is not None else np.zeros(m.nv))
         o.forward()
@@ -50,6 +51,8 @@ def oracle_forward(m, qpos, qvel, act, ctrl, fields, warm=None, use_float=False)
             out[k].append(np.array(o.field(src), dtype=np.float64))
         extra["ncon"].append(o.ncon); extra["nefc"].append(o.nefc)
         extra["niter"].append(int(o.solver_niter[0]))
+        for k in ("ten_wrapadr", "ten_wrapnum", "wrap_obj", "wrap_xpos"):   # tendon path points (mj_tendon)
+            extra[k].append(np.array(o.field(k)))
         extra["contact_geom"].append(np.array(o.contact_geom).reshape(-1, 2))
         extra["contact_dist"].append(np.array(o.contact_dist))
         extra["contact_pos"].append(np.array(o.contact_pos).reshape(-1, 3))

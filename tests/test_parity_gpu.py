@@ -66,6 +66,58 @@ def test_contact_and_row_indices_exact(fwd, name):
                 np.testing.assert_allclose(got.contact_frame.reshape(nw, -1, 9)[w, :n, :3], ex["contact_frame"][w][:, :3], atol=2e-3)
 
 
+def _tendon_paths(adr, num, obj, xpos):
+    """Per tendon: list of (wrap_obj, point).  Zero-length wraps (both tangent points within 1e-4: the straight segment
+    grazes the geom, e.g. finger site 11 lies on the tangent from site 5 to cylinder 4, where float32 and float64 round
+    the wrap / no-wrap decision differently at equal tendon length) are dropped."""
+    xpos = np.asarray(xpos, dtype=np.float64).reshape(-1, 3)
+    paths = []
+    for t in range(len(adr)):
+        pts = [(int(obj[i]), xpos[i]) for i in range(int(adr[t]), int(adr[t]) + int(num[t]))]
+        out, i = [], 0
+        while i < len(pts):
+            if pts[i][0] >= 0 and i + 1 < len(pts) and pts[i + 1][0] == pts[i][0]:
+                if np.abs(pts[i][1] - pts[i + 1][1]).max() > 1e-4:
+                    out += [pts[i], pts[i + 1]]
+                i += 2
+            else:
+                out.append(pts[i]); i += 1
+        paths.append(out)
+    return paths
+
+
+@pytest.mark.parametrize("name", MODELS)
+def test_tendon_path_points(fwd, name):
+    """ten_wrapadr / ten_wrapnum / wrap_obj / wrap_xpos (mj_tendon's path points: sites, tangent points on wrapped geoms,
+    pulley markers, compacted in tendon order): object ids exact, points 1e-5 abs, entries past the last point zero."""
+    m, ref, ex, got, d = fwd(name)
+    if m.ntendon == 0:
+        pytest.skip("no tendons")
+    nw = len(ex["ncon"])
+    assert got.wrap_obj.shape[1:] == (m.nwrap, 2) and got.wrap_xpos.shape[1:] == (m.nwrap, 6)   # mjData shapes
+    wobj, wxpos = got.wrap_obj.reshape(nw, -1), got.wrap_xpos.reshape(nw, -1)
+    identical = 0
+    for w in range(nw):
+        adr, num = got.ten_wrapadr[w], got.ten_wrapnum[w]
+        assert adr[0] == 0 and np.array_equal(adr[1:], np.cumsum(num)[:-1]), "ten_wrapadr is not the running sum of ten_wrapnum"
+        n = int(adr[-1] + num[-1])
+        assert not wobj[w, n:].any() and not wxpos[w, 3 * n:].any(), "entries past the last path point are not zero"
+        identical += int(np.array_equal(num, ex["ten_wrapnum"][w]) and np.array_equal(wobj[w, :n], ex["wrap_obj"][w][:n]))
+        pg = _tendon_paths(adr, num, wobj[w], wxpos[w])
+        po = _tendon_paths(ex["ten_wrapadr"][w], ex["ten_wrapnum"][w], ex["wrap_obj"][w], ex["wrap_xpos"][w])
+        for t in range(m.ntendon):
+            assert [o for o, _ in pg[t]] == [o for o, _ in po[t]], f"world {w} tendon {t}: path objects differ"
+            for (o, a), (_, b) in zip(pg[t], po[t]):
+                if o != -2:   # pulley markers carry no position
+                    np.testing.assert_allclose(a, b, atol=1e-5)
+    if name != "finger":   # the finger model has the systematic grazing wrap described above
+        assert identical >= nw - 1, f"{name}: raw path lists differ from the oracle in {nw - identical} of {nw} worlds"
+    if name in ("hand", "finger", "legs"):
+        assert max(int(x.max()) for x in ex["wrap_obj"]) >= 0, "parity batch has no wrapped geom"
+    if name == "finger":
+        assert min(int(x.min()) for x in ex["wrap_obj"]) == -2, "finger tendons have pulleys"
+
+
 @pytest.mark.parametrize("name", MODELS)
 def test_constrained_acceleration(fwd, models, name):
     """qacc after the Newton solve.  Worlds whose contacts come from the iterative convex narrow phase are sensitive
@@ -166,6 +218,36 @@ def test_fused_substeps_equal_repeated_steps(models):
     torch.cuda.synchronize()
     for f in ("qpos", "qvel", "act", "time", "qacc_warmstart"):
         assert torch.equal(getattr(a, f), getattr(b, f)), f"{f}: fused substeps differ from repeated launches"
+
+
+def test_two_ctas_per_sm_variant_equals_one(models, monkeypatch):
+    """Batches above 8288 worlds run the 8-lane kernel built for two co-resident CTAs per SM (<= 72 registers); it is the
+    same source, so a batch stepped by it must equal the one-CTA build bit for bit.  A large batch picks it by itself."""
+    import torch
+    from myosuite_mjx_b200 import mjx
+    m = models("hand")
+    nw = 96
+    qpos, qvel, act, ctrl = parity.random_state(m, nw, 5, qpos_spread=0.9)
+    model = mjx.put_model(m)
+    import gc
+    names = ("qpos", "qvel", "act", "qacc_warmstart", "actuator_force", "ten_length", "ncon", "nefc", "contact_geom", "efc_force")
+    out = []
+    for ctas in (1, 2):   # one batch alive at a time: a batch holds one of the 8 constant-memory parameter slots
+        monkeypatch.setenv("MYO_TEAM", "8"); monkeypatch.setenv("MYO_CTAS", str(ctas))
+        d = mjx.put_data(model, dict(qpos=qpos, qvel=qvel, act=act, ctrl=ctrl), nworld=nw, fields="all")
+        assert (d.team, d.ctas_per_sm) == (8, ctas)
+        mjx.step(model, d, 3)
+        torch.cuda.synchronize()
+        out.append({f: getattr(d, f).clone() for f in names})
+        del d; gc.collect()
+    for f in names:
+        assert torch.equal(out[0][f], out[1][f]), f"{f}: two-CTA build differs"
+    monkeypatch.delenv("MYO_TEAM"); monkeypatch.delenv("MYO_CTAS")
+    for nworld, want in ((8320, (8, 2)), (8192, (8, 1))):
+        b = mjx.make_data(model, nworld, "core")
+        got = (b.team, b.ctas_per_sm)
+        del b; gc.collect()
+        assert got == want
 
 
 def test_deterministic_and_output_mask_invariant(models):
