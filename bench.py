@@ -204,7 +204,8 @@ def main():
     env_steps = nw * world * args.steps * args.nsub
     value = env_steps / (total_ms * 1e-3)
 
-    # ---- end to end through the C ABI with host buffers (pinned): H2D state+ctrl, step, D2H state, every step
+    # ---- end to end through the C ABI with host buffers (pinned), every step: H2D of the step's input (ctrl; the state is
+    # carried on the device from the previous step, as in the reference's env.step(a) loop), step, D2H of the new state
     # host buffers in the ABI layout [k][nworld]
     hq = torch.empty((m.nq, nw), dtype=torch.float32).pin_memory(); hv = torch.zeros((m.nv, nw), dtype=torch.float32).pin_memory()
     ha = torch.zeros((m.na, nw), dtype=torch.float32).pin_memory(); hc = torch.rand((m.nu, nw), dtype=torch.float32).pin_memory()
@@ -215,7 +216,7 @@ def main():
     e2e_steps = max(10, args.steps // 4)
 
     def host_step():
-        lib.check(L.myo_step_host(d._h, args.nsub, vp(hq.data_ptr()), vp(hv.data_ptr()), vp(ha.data_ptr()), vp(hc.data_ptr()),
+        lib.check(L.myo_step_host(d._h, args.nsub, None, None, None, vp(hc.data_ptr()),
                                   vp(hq.data_ptr()), vp(hv.data_ptr()), vp(ha.data_ptr()), vp(stream.cuda_stream)))
     for _ in range(3):
         host_step()
@@ -225,7 +226,7 @@ def main():
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record(stream)
     for _ in range(e2e_steps):
-        host_step()          # H2D (pinned) -> step -> D2H, synchronises the stream
+        host_step()          # H2D ctrl (pinned) -> step -> D2H qpos / qvel / act, synchronises the stream
     e1.record(stream)
     torch.cuda.synchronize()
     e2e_ms = e0.elapsed_time(e1)
@@ -233,7 +234,7 @@ def main():
     if world > 1:
         dist.all_reduce(te, op=dist.ReduceOp.MAX)
     e2e_value = nw * world * e2e_steps * args.nsub / (float(te.item()) * 1e-3)
-    h2d = nw * (m.nq + m.nv + m.na + m.nu) * 4
+    h2d = nw * m.nu * 4
     d2h = nw * (m.nq + m.nv + m.na) * 4
 
     # ---- optional episode statistics all-reduce: the only collective, off the step path

@@ -119,7 +119,7 @@ struct SmemLayout {
       qacc, warm, tmpv, tforce;
   int counts;    // ncon, nefc, solver_niter of the last forward pass (int bits), read by the wide-output kernel
   // overlay region A (tendon stage)
-  int slots, ulen, uwrap, uwpt, gpre, tmpbody;
+  int slots, ulen, uwrap, uwpt, gpre, upts, tmpbody;
   // overlay region B (collision / constraint / solver stage)
   int cgpose, con, conJ, efc, H, nvec, limrow, basev, cand;
   int nv;        // copy of DevModel.nv (the launch sizes the shared-memory Hessian tiles from it)

@@ -642,7 +642,7 @@ void myo_make_layout(DevModel& D, int nconmax_req, int njmax_req, SmemLayout& L)
   int base = o;
   // overlay A: tendon stage
   L.slots = take(6 * D.nslot); L.ulen = take(D.nunit); L.uwrap = take(D.nunit);
-  L.uwpt = take(6 * D.ngunit); L.gpre = take(D.ngunit + 1);   // tangent points / wrapped-unit prefix counts for the path-point outputs
+  L.uwpt = take(6 * D.ngunit); L.gpre = take(D.ngunit + 1); L.upts = take(6 * D.nunit);   // tangent points / wrapped-unit prefix counts for the path-point outputs
   int endA = o;
   o = base;
   L.tmpbody = take(13 * D.nbody);   // position-output stage only (before the tendon stage)

@@ -613,6 +613,7 @@ __device__ __noinline__ void tendons(int slot, int fslot, SP sm, Tm t, World W) 
     }
     sm[L.ulen + u] = len / D.unit_div[u];
     sm[L.uwrap + u] = wlen < 0.f ? 0.f : 1.f;
+    if (wantw) { st3(sm + L.upts + 6 * u, p0); if (D.unit_end[u]) st3(sm + L.upts + 6 * u + 3, p1); }   // the unit's sites, for the path points
   }
   TSYNC();
   TFOR(n, D.nnz) {
@@ -649,20 +650,16 @@ __device__ __noinline__ void tendons(int slot, int fslot, SP sm, Tm t, World W) 
     }
     TSYNC();
     auto put = [&](int i, f3 p, int obj) {
-      if (wx) { OUTF(wx, 3 * i) = p.x; OUTF(wx, 3 * i + 1) = p.y; OUTF(wx, 3 * i + 2) = p.z; }
+      if (wx) { float* o = (float*)wx + (size_t)(3 * i) * W.nw + W.w; o[0] = p.x; o[W.nw] = p.y; o[2 * W.nw] = p.z; }
       if (wo) OUTI(wo, i) = obj;
     };
     TFOR(u, D.nunit) {
       const int go = D.unit_gord[u], g = D.unit_geom[u];
       const bool wrapped = sm[L.uwrap + u] != 0.f;
       const int off = D.unit_woff[u] + 2 * __float_as_int(sm[L.gpre + go]);
-      const int s0 = D.unit_s0[u], f0 = D.site_frame[s0];
-      put(off, ld3(FR_POS(sm, L, f0)) + mulM(FR_MAT(sm, L, f0), ld3(D.site_lpos + 3 * s0)), -1);
+      put(off, ld3(sm + L.upts + 6 * u), -1);
       if (wrapped) { auto wp = sm + L.uwpt + 6 * go; put(off + 1, ld3(wp), g); put(off + 2, ld3(wp + 3), g); }
-      if (D.unit_end[u]) {
-        const int s1 = D.unit_s1[u], f1 = D.site_frame[s1];
-        put(off + (wrapped ? 3 : 1), ld3(FR_POS(sm, L, f1)) + mulM(FR_MAT(sm, L, f1), ld3(D.site_lpos + 3 * s1)), -1);
-      }
+      if (D.unit_end[u]) put(off + (wrapped ? 3 : 1), ld3(sm + L.upts + 6 * u + 3), -1);
     }
     TFOR(i, D.npulley) put(D.pul_off[i] + 2 * __float_as_int(sm[L.gpre + D.pul_gord[i]]), mk3(0.f, 0.f, 0.f), -2);
     TFOR(k, D.nten) {
