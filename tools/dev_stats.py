@@ -5,7 +5,7 @@ sys.path.insert(0, ROOT)
 import numpy as np, torch
 import bench
 from myosuite_mjx_b200 import mjx
-m = bench.load_model("hand")
+m = bench.load_model(os.environ.get("MODEL", "hand"))
 model = mjx.put_model(m)
 nw = 8192
 q0 = bench.initial_qpos(m, nw, 1234)
