@@ -191,7 +191,7 @@ int myo_batch_create(const myo_model *m, int nworld, int nconmax, int njmax, myo
 void myo_batch_destroy(myo_batch *b);
 int myo_batch_nconmax(const myo_batch *b);
 int myo_batch_njmax(const myo_batch *b);
-int myo_batch_smem_bytes(const myo_batch *b);
+int myo_batch_smem_bytes(const myo_batch *b);   /* bytes of per-world scratch in the library-owned global buffer */
 int myo_batch_team(const myo_batch *b);         /* lanes per world of the kernel variant picked for this batch size (1..16) */
 int myo_batch_ctas_per_sm(const myo_batch *b);  /* co-resident step-kernel CTAs per SM of that variant (2 above 8288 worlds) */
 
@@ -232,7 +232,9 @@ int myo_reset(myo_batch *b, const int32_t *world_mask_dev, void *cuda_stream);
 
 /* Host-buffer convenience used by the end-to-end path: H2D of qpos/qvel/act/ctrl (any may be NULL), step,
  * D2H of qpos/qvel/act, all in the [k][nworld] layout.  Pinned host memory makes the copies asynchronous;
- * synchronises the stream at the end. */
+ * when wide output fields are bound the D2H copies wait for the step kernel only and run on a library-owned side
+ * stream under the wide-output kernel (the state is final by then); the caller's stream joins it and is
+ * synchronised at the end. */
 int myo_step_host(myo_batch *b, int nsubsteps, const float *qpos, const float *qvel, const float *act,
                   const float *ctrl, float *qpos_out, float *qvel_out, float *act_out, void *cuda_stream);
 

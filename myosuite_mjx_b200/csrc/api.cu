@@ -175,6 +175,7 @@ void myo_batch_destroy(myo_batch* b) {
   if (!b) return;
   cudaSetDevice(b->model->device);
   for (void* p : b->owned) cudaFree(p);
+  if (b->copy_stream) { cudaStreamDestroy((cudaStream_t)b->copy_stream); cudaEventDestroy((cudaEvent_t)b->ev_step); cudaEventDestroy((cudaEvent_t)b->ev_copy); }
   if (b->slot >= 0) g_slot_used[b->slot] = false;
   delete b;
 }
@@ -200,7 +201,7 @@ int myo_batch_bind(myo_batch* b, int field, void* dev_ptr, int64_t nbytes) {
   return MYO_OK;
 }
 
-static int launch(myo_batch* b, int nsub, int forward_only, const int32_t* mask, int do_reset, void* stream) {
+static int launch(myo_batch* b, int nsub, int forward_only, const int32_t* mask, int do_reset, void* stream, cudaEvent_t after_step = nullptr) {
   int rc = checkReady(b);
   if (rc) return rc;
   if (b->dirty) {
@@ -228,6 +229,7 @@ static int launch(myo_batch* b, int nsub, int forward_only, const int32_t* mask,
   g_launches++;
   if (b->kern->launch(b->slot, b->L, b->nworld, nsub, forward_only, mask, do_reset, b->scratch, stream) != 0)
     return fail(MYO_ERR_CUDA, std::string("kernel launch failed: ") + cudaGetErrorString(cudaGetLastError()));
+  if (after_step && cudaEventRecord(after_step, (cudaStream_t)stream) != cudaSuccess) return fail(MYO_ERR_CUDA, "event record failed");
   if (b->wide) {
     g_launches++;
     if (myo_out_launch(b->slot, b->nworld, 32 / b->kern->team, mask, forward_only == 2, b->scratch, stream) != 0)
@@ -257,11 +259,29 @@ int myo_step_host(myo_batch* b, int nsubsteps, const float* qpos, const float* q
   if (act && D.na) ok &= cudaMemcpyAsync(b->F.p[MYO_F_ACT], act, n * D.na * 4, cudaMemcpyHostToDevice, s) == cudaSuccess;
   if (ctrl && D.nu) ok &= cudaMemcpyAsync(b->F.p[MYO_F_CTRL], ctrl, n * D.nu * 4, cudaMemcpyHostToDevice, s) == cudaSuccess;
   if (!ok) return fail(MYO_ERR_CUDA, "host-to-device copy failed");
-  rc = myo_step(b, nsubsteps, stream);
+  if (nsubsteps < 1) return fail(MYO_ERR_ARG, "nsubsteps must be >= 1");
+  // qpos / qvel / act are final when the step kernel ends: with wide outputs bound, their copies go to a side stream
+  // that waits for the step kernel only and run under the wide-output kernel; the caller's stream joins before returning.
+  bool fork = false;
+  for (int i = 0; i < kNumWideOutFields; i++) fork |= b->F.p[kWideOutFields[i]] != nullptr;
+  if (fork && !b->copy_stream) {
+    cudaStream_t cs; cudaEvent_t e0, e1;
+    if (cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking) != cudaSuccess || cudaEventCreateWithFlags(&e0, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&e1, cudaEventDisableTiming) != cudaSuccess)
+      return fail(MYO_ERR_CUDA, "side stream creation failed");
+    b->copy_stream = cs; b->ev_step = e0; b->ev_copy = e1;
+  }
+  rc = launch(b, nsubsteps, 0, nullptr, 0, stream, fork ? (cudaEvent_t)b->ev_step : nullptr);
   if (rc) return rc;
-  if (qpos_out) ok &= cudaMemcpyAsync(qpos_out, b->F.p[MYO_F_QPOS], n * D.nq * 4, cudaMemcpyDeviceToHost, s) == cudaSuccess;
-  if (qvel_out) ok &= cudaMemcpyAsync(qvel_out, b->F.p[MYO_F_QVEL], n * D.nv * 4, cudaMemcpyDeviceToHost, s) == cudaSuccess;
-  if (act_out && D.na) ok &= cudaMemcpyAsync(act_out, b->F.p[MYO_F_ACT], n * D.na * 4, cudaMemcpyDeviceToHost, s) == cudaSuccess;
+  cudaStream_t cs = fork ? (cudaStream_t)b->copy_stream : s;
+  if (fork) ok &= cudaStreamWaitEvent(cs, (cudaEvent_t)b->ev_step, 0) == cudaSuccess;
+  if (qpos_out) ok &= cudaMemcpyAsync(qpos_out, b->F.p[MYO_F_QPOS], n * D.nq * 4, cudaMemcpyDeviceToHost, cs) == cudaSuccess;
+  if (qvel_out) ok &= cudaMemcpyAsync(qvel_out, b->F.p[MYO_F_QVEL], n * D.nv * 4, cudaMemcpyDeviceToHost, cs) == cudaSuccess;
+  if (act_out && D.na) ok &= cudaMemcpyAsync(act_out, b->F.p[MYO_F_ACT], n * D.na * 4, cudaMemcpyDeviceToHost, cs) == cudaSuccess;
+  if (fork) {
+    ok &= cudaEventRecord((cudaEvent_t)b->ev_copy, cs) == cudaSuccess;
+    ok &= cudaStreamWaitEvent(s, (cudaEvent_t)b->ev_copy, 0) == cudaSuccess;
+  }
   if (!ok || cudaStreamSynchronize(s) != cudaSuccess) return fail(MYO_ERR_CUDA, std::string("device-to-host copy failed: ") + cudaGetErrorString(cudaGetLastError()));
   return MYO_OK;
 }

@@ -50,6 +50,9 @@ struct myo_batch {
   const TeamVariant* kern;   // step kernel variant (lanes per world) chosen for this batch size
   bool dirty;    // parameters changed since the last upload
   bool wide;     // some wide output field is bound: the output kernel runs after the step kernel
+  // myo_step_host: the state is final when the step kernel ends, so its device-to-host copies run on a side stream
+  // under the wide-output kernel (created on first use)
+  void* copy_stream = nullptr; void* ev_step = nullptr; void* ev_copy = nullptr;
   void* wrap_cleared[2] = {nullptr, nullptr};   // wrap_obj / wrap_xpos buffers already zeroed once (api.cu launch)
   float* scratch; // per-world intermediates, [nwarps][L.total][worlds per warp]
   std::vector<void*> owned;

@@ -404,24 +404,27 @@ def test_full_size_properties(models):
     assert float((d.qpos - hi).max()) < 0.3 and float((lo - d.qpos).max()) < 0.3      # soft limits hold
 
 
-def test_step_host_round_trip(models):
+@pytest.mark.parametrize("fields", ["core", "all"])   # "all": the state copies run on the side stream under the wide-output kernel
+def test_step_host_round_trip(models, fields):
     import ctypes
     import torch
     from myosuite_mjx_b200 import lib, mjx
     m = models("elbow")
     model = mjx.put_model(m)
     nw = 128
-    d = mjx.make_data(model, nw, fields="core")
-    e = mjx.make_data(model, nw, fields="core")
+    d = mjx.make_data(model, nw, fields=fields)
+    e = mjx.make_data(model, nw, fields=fields)
     # host buffers in the ABI layout [k][nworld]
     hq = torch.full((1, nw), 0.4).pin_memory(); hv = torch.zeros((1, nw)).pin_memory()
     ha = torch.zeros((m.na, nw)).pin_memory(); hc = torch.rand((m.nu, nw)).pin_memory()
     oq = torch.empty_like(hq).pin_memory(); ov = torch.empty_like(hv).pin_memory(); oa = torch.empty_like(ha).pin_memory()
     vp = ctypes.c_void_p
-    lib.check(lib.lib().myo_step_host(d._h, 3, vp(hq.data_ptr()), vp(hv.data_ptr()), vp(ha.data_ptr()), vp(hc.data_ptr()),
-                                      vp(oq.data_ptr()), vp(ov.data_ptr()), vp(oa.data_ptr()), None))
+    for rep in range(3):   # repeated calls reuse the side stream and its events
+        lib.check(lib.lib().myo_step_host(d._h, 3, vp(hq.data_ptr()) if rep == 0 else None, vp(hv.data_ptr()) if rep == 0 else None,
+                                          vp(ha.data_ptr()) if rep == 0 else None, vp(hc.data_ptr()),
+                                          vp(oq.data_ptr()), vp(ov.data_ptr()), vp(oa.data_ptr()), None))
     e.storage("qpos").copy_(hq.cuda()); e.storage("ctrl").copy_(hc.cuda())
-    mjx.step(model, e, 3)
+    mjx.step(model, e, 9)
     torch.cuda.synchronize()
     assert torch.equal(oq, e.storage("qpos").cpu()) and torch.equal(ov, e.storage("qvel").cpu()) and torch.equal(oa, e.storage("act").cpu())
 
