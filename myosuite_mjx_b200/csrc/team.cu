@@ -1244,6 +1244,9 @@ __device__ __noinline__ int collision(int slot, SP sm, Tm t, int* status) {
         auto c = sm + L.con + 12 * at; auto o = tmp + 16 * k + 1 + 7 * q;
         for (int e = 0; e < 7; e++) c[e] = o[e];
         c[7] = __int_as_float(pr); c[8] = __int_as_float(-1); c[9] = __int_as_float(D.pair_dim[pr]);
+        // dofs that move exactly one of the two bodies (static per pair): the only non-zero columns of the contact's rows
+        const int f1 = D.cg_frame[D.pair_cg1[pr]], f2 = D.cg_frame[D.pair_cg2[pr]];
+        c[10] = __int_as_float(D.fr_mask[2 * f1] ^ D.fr_mask[2 * f2]); c[11] = __int_as_float(D.fr_mask[2 * f1 + 1] ^ D.fr_mask[2 * f2 + 1]);
       }
       ncon += total;
     }
@@ -1377,14 +1380,15 @@ __device__ __noinline__ int makeConstraint(int slot, SP sm, Tm t, int ncon, int*
     TFOR(idx, ncon * nv) {
       const int c = idx / nv, k = idx - c * nv;
       auto cr = sm + L.con + 12 * c;
-      const int pr = __float_as_int(cr[7]);
-      const int f1 = D.cg_frame[D.pair_cg1[pr]], f2 = D.cg_frame[D.pair_cg2[pr]];
-      const int in1 = (D.fr_mask[2 * f1 + (k >> 5)] >> (k & 31)) & 1, in2 = (D.fr_mask[2 * f2 + (k >> 5)] >> (k & 31)) & 1;
       auto J = sm + L.conJ + (c * nb) * nv + k;
-      if (in1 == in2) { J[0] = 0.f; if (nb > 1) { J[nv] = 0.f; J[2 * nv] = 0.f; } if (nb > 3) J[3 * nv] = 0.f; continue; }
+      if (!(((unsigned)__float_as_int(cr[10 + (k >> 5)]) >> (k & 31)) & 1u)) {   // dof k moves both bodies or neither
+        J[0] = 0.f; if (nb > 1) { J[nv] = 0.f; J[2 * nv] = 0.f; } if (nb > 3) J[3 * nv] = 0.f; continue;
+      }
+      const int f1 = D.cg_frame[D.pair_cg1[__float_as_int(cr[7])]];
+      const int in1 = (D.fr_mask[2 * f1 + (k >> 5)] >> (k & 31)) & 1;   // it moves exactly one of them: the first (-) or the second (+)
       const f3 pos = ld3(cr + 1), n = ld3(cr + 4);
       f3 y, z; makeFrame(n, &y, &z);
-      const float sgn = (float)(in2 - in1);
+      const float sgn = in1 ? -1.f : 1.f;
       auto cd = sm + L.cdof + 6 * k;
       const f3 jr = ld3(cd) * sgn;
       const f3 jp = (ld3(cd + 3) + cross(ld3(cd), pos - ld3(sm + L.rootcom + 3 * D.fr_root[D.dof_frame[k]]))) * sgn;
@@ -1556,9 +1560,7 @@ __device__ __noinline__ void hessianFactor(int slot, SP sm, Tm t, int ncon, int 
     // The contact Jacobian is non-zero only on dofs that move exactly one of the two bodies: that bit set is static per
     // pair.  Lane tl owns the tl-th, (tl + TEAM)-th ... set bit as a row of H and finds it directly (__fns), so the
     // lanes of a team work on their rows at the same time; columns are the set bits up to the row.
-    const int pr = __float_as_int(cr[7]);
-    const int f1 = D.cg_frame[D.pair_cg1[pr]], f2 = D.cg_frame[D.pair_cg2[pr]];
-    const unsigned mlo = (unsigned)(D.fr_mask[2 * f1] ^ D.fr_mask[2 * f2]), mhi = (unsigned)(D.fr_mask[2 * f1 + 1] ^ D.fr_mask[2 * f2 + 1]);
+    const unsigned mlo = (unsigned)__float_as_int(cr[10]), mhi = (unsigned)__float_as_int(cr[11]);   // collision() stored the pair's dof set
     const int nlo = __popc(mlo), nrow = nlo + __popc(mhi);
     #pragma unroll 1
     for (int a = t.tl; a < nrow; a += TEAM) {
