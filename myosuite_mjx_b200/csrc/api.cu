@@ -212,7 +212,9 @@ static int launch(myo_batch* b, int nsub, int forward_only, const int32_t* mask,
     if (wide_on)
       for (int i = 0; i < kNumWideOutFields; i++)
         if (b->F.p[kWideOutFields[i]]) { Fstep.p[kWideOutFields[i]] = nullptr; b->wide = true; }
-    if (b->kern->upload(b->slot, b->D, b->L, Fstep, stream) != 0) return fail(MYO_ERR_CUDA, "parameter upload failed");
+    SmemLayout Ls = b->L;
+    Ls.wantw = b->F.p[MYO_F_WRAP_XPOS] || b->F.p[MYO_F_WRAP_OBJ] || b->F.p[MYO_F_TEN_WRAPADR] || b->F.p[MYO_F_TEN_WRAPNUM];
+    if (b->kern->upload(b->slot, b->D, Ls, Fstep, stream) != 0) return fail(MYO_ERR_CUDA, "parameter upload failed");
     if (b->wide && myo_out_upload(b->slot, b->D, b->L, b->F, stream) != 0) return fail(MYO_ERR_CUDA, "parameter upload failed");
     // Path-point buffers: the kernel clears only the entries a wrap state can reach; the rest of a newly bound buffer is
     // zeroed here once (mj_makeData's zeros), on the caller's stream.

@@ -124,6 +124,7 @@ struct SmemLayout {
   int cgpose, con, conJ, efc, H, nvec, limrow, basev, cand;
   int nv;        // copy of DevModel.nv (the launch sizes the shared-memory Hessian tiles from it)
   int hshared;   // set by the kernel variant at upload: Newton Hessian tiles live in shared memory
+  int wantw;     // set at upload: a path-point field is bound, the tendon stage keeps tangent points and wrap counts
 };
 
 #endif  // MYO_DEVMODEL_H_

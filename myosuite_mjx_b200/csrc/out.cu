@@ -8,6 +8,7 @@
 //   qM                                                                          (mj_crb, dense symmetric)
 //   efc_J                                                                       (mj_makeConstraint, dense rows)
 //   contact_* , efc_pos/margin/D/aref/force/type, xanchor, xaxis, cdof          (small per-row copies)
+//   ten_wrapadr, ten_wrapnum, wrap_obj, wrap_xpos                               (mj_tendon's path points)
 // Same arithmetic, in the same order, as the step kernel's own writers for these fields (which remain in team.cu and
 // run when this kernel is switched off with MYO_WIDE_OUT=0).
 #include <cuda_runtime.h>
@@ -81,16 +82,21 @@ __global__ void __launch_bounds__(OUT_THREADS, OUT_MINBLOCKS) outKernel(int slot
   void* epos = F.p[MYO_F_EFC_POS]; void* emar = F.p[MYO_F_EFC_MARGIN]; void* eD = F.p[MYO_F_EFC_D]; void* earef = F.p[MYO_F_EFC_AREF];
   void* efrc = F.p[MYO_F_EFC_FORCE]; void* etyp = F.p[MYO_F_EFC_TYPE];
   void* xa = F.p[MYO_F_XANCHOR]; void* xx = F.p[MYO_F_XAXIS]; void* cdo = F.p[MYO_F_CDOF];
+  void* wxp = F.p[MYO_F_WRAP_XPOS]; void* wob = F.p[MYO_F_WRAP_OBJ]; void* wad = F.p[MYO_F_TEN_WRAPADR]; void* wnu = F.p[MYO_F_TEN_WRAPNUM];
+  const bool wpts = wxp || wob;
   const int n0 = (sp || smt) ? D.nsite : 0, n1 = n0 + ((gp || gm) ? D.ngeom : 0),
             n2 = n1 + ((xpos || xquat || xmat || xipos || ximat) ? D.nbody : 0), n3 = n2 + (tj ? D.nten : 0), n4 = n3 + (am ? D.nu : 0),
             n5 = n4 + (qMo ? nv : 0), n6 = n5 + (eJ ? D.njmax : 0),
             n7 = n6 + ((cg || cdim || cadr || cdist || cpos || cfr || cinc || cfri || csr || csi) ? D.nconmax : 0),
             n8 = n7 + ((epos || emar || eD || earef || efrc || etyp) ? D.njmax : 0), n9 = n8 + ((xa || xx) ? D.njnt : 0),
-            n10 = n9 + (cdo ? nv : 0);
+            n10 = n9 + (cdo ? nv : 0),
+            // tendon path points: one item per path unit, pulley marker, tendon, and clearable entry past the last point
+            n11 = n10 + (wpts ? D.nunit : 0), n12 = n11 + (wpts ? D.npulley : 0), n13 = n12 + ((wad || wnu) ? D.nten : 0),
+            n14 = n13 + (wpts ? 2 * D.ngunit : 0);
   const int ncon = __float_as_int(S(c, L.counts));
   const int nefc = __float_as_int(S(c, L.counts + 1));   // left by the step kernel: ncon, nefc, niter
   const size_t nw = c.nw, w = c.w;
-  for (int it = blockIdx.y; it < n10; it += gridDim.y) {
+  for (int it = blockIdx.y; it < n14; it += gridDim.y) {
     if (posvel && it >= n4 && it < n8) continue;   // position / velocity refresh: inertia, contacts and constraint rows are not recomputed
     if (it < n1) {   // site or geom pose
       const bool site = it < n0;
@@ -251,11 +257,49 @@ __global__ void __launch_bounds__(OUT_THREADS, OUT_MINBLOCKS) outKernel(int slot
       const int j = it - n8;
       if (xa) { Row o(xa, 3 * (size_t)j, nw, w); for (int k = 0; k < 3; k++) o.put(S(c, L.xanchor + 3 * j + k)); }
       if (xx) { Row o(xx, 3 * (size_t)j, nw, w); for (int k = 0; k < 3; k++) o.put(S(c, L.xaxis + 3 * j + k)); }
-    } else {
+    } else if (it < n10) {
       const int i = it - n9;
       Row o(cdo, 6 * (size_t)i, nw, w);
 #pragma unroll
       for (int k = 0; k < 6; k++) o.put(S(c, L.cdof + 6 * i + k));
+    } else {
+      // mj_tendon's path points in MuJoCo's compacted order (team.cu tendons() has the same writer for MYO_WIDE_OUT=0):
+      // entry index = static offset (every unit unwrapped) + 2 x wrapped geom units before the item (scratch gpre)
+      auto putpt = [&](int i, float x, float y, float z, int obj) {
+        if (wxp) { Row o(wxp, 3 * (size_t)i, nw, w); o.put(x); o.put(y); o.put(z); }
+        if (wob) Row(wob, i, nw, w).puti(obj);
+      };
+      if (it < n11) {
+        const int u = it - n10, go = D.unit_gord[u], g = D.unit_geom[u];
+        const int pre = __float_as_int(S(c, L.gpre + go));
+        const bool wrapped = g >= 0 && __float_as_int(S(c, L.gpre + go + 1)) != pre;
+        const int off = D.unit_woff[u] + 2 * pre;
+        float p[3], R[9];
+        const int s0 = D.unit_s0[u];
+        framePose(c, L, D.site_frame[s0], D.site_lpos + 3 * s0, nullptr, p, nullptr, R);
+        putpt(off, p[0], p[1], p[2], -1);
+        if (wrapped) {
+          const int wp = L.uwpt + 6 * go;
+          putpt(off + 1, S(c, wp), S(c, wp + 1), S(c, wp + 2), g);
+          putpt(off + 2, S(c, wp + 3), S(c, wp + 4), S(c, wp + 5), g);
+        }
+        if (D.unit_end[u]) {
+          const int s1 = D.unit_s1[u];
+          framePose(c, L, D.site_frame[s1], D.site_lpos + 3 * s1, nullptr, p, nullptr, R);
+          putpt(off + (wrapped ? 3 : 1), p[0], p[1], p[2], -1);
+        }
+      } else if (it < n12) {
+        const int i = it - n11;
+        putpt(D.pul_off[i] + 2 * __float_as_int(S(c, L.gpre + D.pul_gord[i])), 0.f, 0.f, 0.f, -2);
+      } else if (it < n13) {
+        const int k = it - n12;
+        const int g0 = __float_as_int(S(c, L.gpre + D.ten_gord[k])), g1 = __float_as_int(S(c, L.gpre + D.ten_gord[k + 1]));
+        if (wad) Row(wad, k, nw, w).puti(D.ten_woff[k] + 2 * g0);
+        if (wnu) Row(wnu, k, nw, w).puti(D.ten_woff[k + 1] - D.ten_woff[k] + 2 * (g1 - g0));
+      } else {   // entries a fuller wrap state of an earlier step can have written
+        const int i = it - n13;
+        if (i >= 2 * __float_as_int(S(c, L.gpre + D.ngunit))) putpt(D.ten_woff[D.nten] + i, 0.f, 0.f, 0.f, 0);
+      }
     }
   }
 }
@@ -267,7 +311,7 @@ const int kWideOutFields[] = {MYO_F_SITE_XPOS, MYO_F_SITE_XMAT, MYO_F_GEOM_XPOS,
                               MYO_F_CONTACT_GEOM, MYO_F_CONTACT_DIM, MYO_F_CONTACT_EFC_ADDRESS, MYO_F_CONTACT_DIST, MYO_F_CONTACT_POS,
                               MYO_F_CONTACT_FRAME, MYO_F_CONTACT_INCLUDEMARGIN, MYO_F_CONTACT_FRICTION, MYO_F_CONTACT_SOLREF,
                               MYO_F_CONTACT_SOLIMP, MYO_F_EFC_POS, MYO_F_EFC_MARGIN, MYO_F_EFC_D, MYO_F_EFC_AREF, MYO_F_EFC_FORCE,
-                              MYO_F_EFC_TYPE, MYO_F_XANCHOR, MYO_F_XAXIS, MYO_F_CDOF};
+                              MYO_F_EFC_TYPE, MYO_F_XANCHOR, MYO_F_XAXIS, MYO_F_CDOF, MYO_F_WRAP_XPOS, MYO_F_WRAP_OBJ, MYO_F_TEN_WRAPADR, MYO_F_TEN_WRAPNUM};
 const int kNumWideOutFields = sizeof(kWideOutFields) / sizeof(int);
 
 int myo_out_upload(int slot, const DevModel& D, const SmemLayout& L, const FieldPtrs& F, void* stream) {

@@ -639,10 +639,14 @@ void myo_make_layout(DevModel& D, int nconmax_req, int njmax_req, SmemLayout& L)
   L.bias = take(nv); L.passive = take(nv); L.qfrc_act = take(nv); L.smooth = take(nv); L.qfrc_con = take(nv);
   L.qacc_smooth = take(nv); L.qacc = take(nv); L.warm = take(nv); L.tmpv = take(nv); L.tforce = take(D.nten);
   L.counts = take(4);
+  // path points (persistent: the wide-output kernel reads them after the step): tangent points of the wrapped units and the
+  // running count of wrapped geom units
+  L.uwpt = take(6 * D.ngunit); L.gpre = take(D.ngunit + 1);
+  L.wantw = 0;
   int base = o;
   // overlay A: tendon stage
   L.slots = take(6 * D.nslot); L.ulen = take(D.nunit); L.uwrap = take(D.nunit);
-  L.uwpt = take(6 * D.ngunit); L.gpre = take(D.ngunit + 1); L.upts = take(6 * D.nunit);   // tangent points / wrapped-unit prefix counts for the path-point outputs
+  L.upts = take(6 * D.nunit);   // the units' site positions, for the step kernel's own path-point writer   // tangent points / wrapped-unit prefix counts for the path-point outputs
   int endA = o;
   o = base;
   L.tmpbody = take(13 * D.nbody);   // position-output stage only (before the tendon stage)

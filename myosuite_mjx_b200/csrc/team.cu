@@ -582,7 +582,8 @@ __device__ __noinline__ float wrapGeom(f3 x0, f3 x1, f3 gpos, const float* gmat,
 __device__ __noinline__ void tendons(int slot, int fslot, SP sm, Tm t, World W) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L; const FieldPtrs& F = tP[fslot].F;
   void* wx = F.p[MYO_F_WRAP_XPOS]; void* wo = F.p[MYO_F_WRAP_OBJ]; void* wa = F.p[MYO_F_TEN_WRAPADR]; void* wn = F.p[MYO_F_TEN_WRAPNUM];
-  const bool wantw = wx || wo || wa || wn;   // mjData path points requested
+  const bool wrout = wx || wo || wa || wn;                 // path points written here (the wide-output kernel is off)
+  const bool wantw = wrout || (L.wantw && fslot == slot);   // path points requested: keep tangent points and wrap counts
   TFOR(uo, D.nunit) {
     const int u = D.unit_order[uo];
     const int s0 = D.unit_s0[u], s1 = D.unit_s1[u], g = D.unit_geom[u];
@@ -613,7 +614,7 @@ __device__ __noinline__ void tendons(int slot, int fslot, SP sm, Tm t, World W) 
     }
     sm[L.ulen + u] = len / D.unit_div[u];
     sm[L.uwrap + u] = wlen < 0.f ? 0.f : 1.f;
-    if (wantw) { st3(sm + L.upts + 6 * u, p0); if (D.unit_end[u]) st3(sm + L.upts + 6 * u + 3, p1); }   // the unit's sites, for the path points
+    if (wrout) { st3(sm + L.upts + 6 * u, p0); if (D.unit_end[u]) st3(sm + L.upts + 6 * u + 3, p1); }   // the unit's sites, for the path points
   }
   TSYNC();
   TFOR(n, D.nnz) {
@@ -649,6 +650,9 @@ __device__ __noinline__ void tendons(int slot, int fslot, SP sm, Tm t, World W) 
       sm[L.gpre + ngu] = __int_as_float(acc);
     }
     TSYNC();
+  }
+  if (wrout) {
+    const int ngu = D.ngunit;
     auto put = [&](int i, f3 p, int obj) {
       if (wx) { float* o = (float*)wx + (size_t)(3 * i) * W.nw + W.w; o[0] = p.x; o[W.nw] = p.y; o[2 * W.nw] = p.z; }
       if (wo) OUTI(wo, i) = obj;
