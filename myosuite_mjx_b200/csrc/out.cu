@@ -84,6 +84,7 @@ __global__ void __launch_bounds__(OUT_THREADS, OUT_MINBLOCKS) outKernel(int slot
   void* xa = F.p[MYO_F_XANCHOR]; void* xx = F.p[MYO_F_XAXIS]; void* cdo = F.p[MYO_F_CDOF];
   void* wxp = F.p[MYO_F_WRAP_XPOS]; void* wob = F.p[MYO_F_WRAP_OBJ]; void* wad = F.p[MYO_F_TEN_WRAPADR]; void* wnu = F.p[MYO_F_TEN_WRAPNUM];
   const bool wpts = wxp || wob;
+  void* qLDo = F.p[MYO_F_QLD]; void* cvo = F.p[MYO_F_CVEL]; void* cdd = F.p[MYO_F_CDOF_DOT];
   const int n0 = (sp || smt) ? D.nsite : 0, n1 = n0 + ((gp || gm) ? D.ngeom : 0),
             n2 = n1 + ((xpos || xquat || xmat || xipos || ximat) ? D.nbody : 0), n3 = n2 + (tj ? D.nten : 0), n4 = n3 + (am ? D.nu : 0),
             n5 = n4 + (qMo ? nv : 0), n6 = n5 + (eJ ? D.njmax : 0),
@@ -92,12 +93,13 @@ __global__ void __launch_bounds__(OUT_THREADS, OUT_MINBLOCKS) outKernel(int slot
             n10 = n9 + (cdo ? nv : 0),
             // tendon path points: one item per path unit, pulley marker, tendon, and clearable entry past the last point
             n11 = n10 + (wpts ? D.nunit : 0), n12 = n11 + (wpts ? D.npulley : 0), n13 = n12 + ((wad || wnu) ? D.nten : 0),
-            n14 = n13 + (wpts ? 2 * D.ngunit : 0);
+            n14 = n13 + (wpts ? 2 * D.ngunit : 0),
+            n15 = n14 + (cvo ? D.nbody : 0), n16 = n15 + (cdd ? nv : 0), n17 = n16 + (qLDo ? nv : 0);
   const int ncon = __float_as_int(S(c, L.counts));
   const int nefc = __float_as_int(S(c, L.counts + 1));   // left by the step kernel: ncon, nefc, niter
   const size_t nw = c.nw, w = c.w;
-  for (int it = blockIdx.y; it < n14; it += gridDim.y) {
-    if (posvel && it >= n4 && it < n8) continue;   // position / velocity refresh: inertia, contacts and constraint rows are not recomputed
+  for (int it = blockIdx.y; it < n17; it += gridDim.y) {
+    if (posvel && ((it >= n4 && it < n8) || it >= n16)) continue;   // position / velocity refresh: inertia, contacts and constraint rows are not recomputed
     if (it < n1) {   // site or geom pose
       const bool site = it < n0;
       const int q = site ? it : it - n0;
@@ -262,6 +264,24 @@ __global__ void __launch_bounds__(OUT_THREADS, OUT_MINBLOCKS) outKernel(int slot
       Row o(cdo, 6 * (size_t)i, nw, w);
 #pragma unroll
       for (int k = 0; k < 6; k++) o.put(S(c, L.cdof + 6 * i + k));
+    } else if (it >= n14) {
+      if (it < n15) {          // cvel of body b = that of its frame
+        const int b = it - n14, o_ = L.cvel + 6 * D.body_frame[b];
+        Row o(cvo, 6 * (size_t)b, nw, w);
+#pragma unroll
+        for (int k = 0; k < 6; k++) o.put(S(c, o_ + k));
+      } else if (it < n16) {
+        const int i = it - n15;
+        Row o(cdd, 6 * (size_t)i, nw, w);
+#pragma unroll
+        for (int k = 0; k < 6; k++) o.put(S(c, L.cdof_dot + 6 * i + k));
+      } else {                 // dense qLD row: zeros, then the dof's ancestor chain (lower triangle of the L^T D L factor)
+        const int i = it - n16;
+        { Row o(qLDo, (size_t)i * nv, nw, w); for (int k = 0; k < nv; k++) o.put(0.f); }
+        float* row = (float*)qLDo + (size_t)i * nv * nw + w;
+        const int a = D.dof_Madr[i], d = D.dof_rowlen[i];
+        for (int q = 0; q < d; q++) row[(size_t)D.M_col[a + q] * nw] = S(c, L.qLD + a + q);
+      }
     } else {
       // mj_tendon's path points in MuJoCo's compacted order (team.cu tendons() has the same writer for MYO_WIDE_OUT=0):
       // entry index = static offset (every unit unwrapped) + 2 x wrapped geom units before the item (scratch gpre)
@@ -311,7 +331,8 @@ const int kWideOutFields[] = {MYO_F_SITE_XPOS, MYO_F_SITE_XMAT, MYO_F_GEOM_XPOS,
                               MYO_F_CONTACT_GEOM, MYO_F_CONTACT_DIM, MYO_F_CONTACT_EFC_ADDRESS, MYO_F_CONTACT_DIST, MYO_F_CONTACT_POS,
                               MYO_F_CONTACT_FRAME, MYO_F_CONTACT_INCLUDEMARGIN, MYO_F_CONTACT_FRICTION, MYO_F_CONTACT_SOLREF,
                               MYO_F_CONTACT_SOLIMP, MYO_F_EFC_POS, MYO_F_EFC_MARGIN, MYO_F_EFC_D, MYO_F_EFC_AREF, MYO_F_EFC_FORCE,
-                              MYO_F_EFC_TYPE, MYO_F_XANCHOR, MYO_F_XAXIS, MYO_F_CDOF, MYO_F_WRAP_XPOS, MYO_F_WRAP_OBJ, MYO_F_TEN_WRAPADR, MYO_F_TEN_WRAPNUM};
+                              MYO_F_EFC_TYPE, MYO_F_XANCHOR, MYO_F_XAXIS, MYO_F_CDOF, MYO_F_WRAP_XPOS, MYO_F_WRAP_OBJ, MYO_F_TEN_WRAPADR, MYO_F_TEN_WRAPNUM,
+                              MYO_F_CVEL, MYO_F_CDOF_DOT, MYO_F_QLD};
 const int kNumWideOutFields = sizeof(kWideOutFields) / sizeof(int);
 
 int myo_out_upload(int slot, const DevModel& D, const SmemLayout& L, const FieldPtrs& F, void* stream) {

@@ -633,7 +633,7 @@ void myo_make_layout(DevModel& D, int nconmax_req, int njmax_req, SmemLayout& L)
   L.frames = take(16 * D.nframe); L.xanchor = take(3 * D.njnt); L.xaxis = take(3 * D.njnt); L.rootcom = take(3 * D.nroot);
   L.cinert = take(10 * D.nframe); L.crb = take(10 * D.nframe); L.cdof = take(6 * nv); L.cdof_dot = take(6 * nv);
   L.cvel = take(6 * D.nframe); L.cacc = take(6 * D.nframe);
-  L.qM = take(D.nM); L.qLD = take(D.nM); L.qLDinv = take(nv); L.qH = L.qLD; L.qHinv = L.qLDinv;
+  L.qM = take(D.nM); L.qLD = take(D.nM); L.qLDinv = take(nv); L.qH = take(D.nM); L.qHinv = take(nv);   // qH: Euler's M + h B factor; qLD stays for the wide-output kernel
   L.tenlen = take(D.nten); L.tenvel = take(D.nten); L.tenJ = take(D.nnz);
   L.actlen = take(D.nu); L.actvel = take(D.nu); L.actforce = take(D.nu); L.actdot = take(D.na);
   L.bias = take(nv); L.passive = take(nv); L.qfrc_act = take(nv); L.smooth = take(nv); L.qfrc_con = take(nv);
