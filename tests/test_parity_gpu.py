@@ -118,6 +118,29 @@ def test_tendon_path_points(fwd, name):
         assert min(int(x.min()) for x in ex["wrap_obj"]) == -2, "finger tendons have pulleys"
 
 
+def test_tendon_path_points_shrink_cleanly(models):
+    """A world whose wrap state loses wraps between two passes leaves no stale path points behind: after the second
+    forward pass the arrays equal those of a fresh batch at the same state (wide-output kernel and the step kernel's own writer)."""
+    import torch
+    from myosuite_mjx_b200 import mjx
+    m = models("hand")
+    nw = 64
+    qa, qvel, act, ctrl = parity.random_state(m, nw, 21, qpos_spread=0.9)
+    qb = parity.random_state(m, nw, 22, qpos_spread=0.2)[0]
+    model = mjx.put_model(m)
+    d = mjx.put_data(model, dict(qpos=qa, qvel=qvel, act=act, ctrl=ctrl), nworld=nw, fields="all")
+    mjx.forward(model, d)
+    na = d.ten_wrapnum.sum(dim=1).clone()
+    d.storage("qpos").copy_(torch.as_tensor(qb.T, dtype=torch.float32, device="cuda"))
+    mjx.forward(model, d)
+    e = mjx.put_data(model, dict(qpos=qb, qvel=qvel, act=act, ctrl=ctrl), nworld=nw, fields="all")
+    mjx.forward(model, e)
+    torch.cuda.synchronize()
+    assert (d.ten_wrapnum.sum(dim=1) < na).any(), "no world lost a wrap between the two states"
+    for f in ("ten_wrapadr", "ten_wrapnum", "wrap_obj", "wrap_xpos"):
+        assert torch.equal(getattr(d, f), getattr(e, f)), f"{f}: stale entries after the wrap state shrank"
+
+
 @pytest.mark.parametrize("name", MODELS)
 def test_constrained_acceleration(fwd, models, name):
     """qacc after the Newton solve.  Worlds whose contacts come from the iterative convex narrow phase are sensitive
