@@ -158,6 +158,9 @@ int myo_batch_create(const myo_model* m, int nworld, int nconmax, int njmax, myo
   {
     void* p = nullptr;
     b->kern = pickVariant(nworld);
+    b->kern_fused = b->kern;
+    if (b->kern->ctas_per_sm > 1 && !getenv("MYO_CTAS"))
+      for (const TeamVariant& v : kVariants) if (v.team == b->kern->team && v.ctas_per_sm == 1) b->kern_fused = &v;   // same scratch layout
     if (cudaMalloc(&p, b->kern->scratch_floats(b->L, nworld) * sizeof(float)) != cudaSuccess) { g_slot_used[b->slot] = false; delete b; return fail(MYO_ERR_CUDA, "cudaMalloc of the per-world scratch failed"); }
     b->owned.push_back(p); b->scratch = (float*)p;
   }
@@ -215,6 +218,7 @@ static int launch(myo_batch* b, int nsub, int forward_only, const int32_t* mask,
     SmemLayout Ls = b->L;
     Ls.wantw = b->F.p[MYO_F_WRAP_XPOS] || b->F.p[MYO_F_WRAP_OBJ] || b->F.p[MYO_F_TEN_WRAPADR] || b->F.p[MYO_F_TEN_WRAPNUM];
     if (b->kern->upload(b->slot, b->D, Ls, Fstep, stream) != 0) return fail(MYO_ERR_CUDA, "parameter upload failed");
+    if (b->kern_fused != b->kern && b->kern_fused->upload(b->slot, b->D, Ls, Fstep, stream) != 0) return fail(MYO_ERR_CUDA, "parameter upload failed");
     if (b->wide && myo_out_upload(b->slot, b->D, b->L, b->F, stream) != 0) return fail(MYO_ERR_CUDA, "parameter upload failed");
     // Path-point buffers: the kernel clears only the entries a wrap state can reach; the rest of a newly bound buffer is
     // zeroed here once (mj_makeData's zeros), on the caller's stream.
@@ -229,7 +233,8 @@ static int launch(myo_batch* b, int nsub, int forward_only, const int32_t* mask,
     b->dirty = false;
   }
   g_launches++;
-  if (b->kern->launch(b->slot, b->L, b->nworld, nsub, forward_only, mask, do_reset, b->scratch, stream) != 0)
+  const TeamVariant* kern = (!forward_only && nsub >= 3) ? b->kern_fused : b->kern;
+  if (kern->launch(b->slot, b->L, b->nworld, nsub, forward_only, mask, do_reset, b->scratch, stream) != 0)
     return fail(MYO_ERR_CUDA, std::string("kernel launch failed: ") + cudaGetErrorString(cudaGetLastError()));
   if (after_step && cudaEventRecord(after_step, (cudaStream_t)stream) != cudaSuccess) return fail(MYO_ERR_CUDA, "event record failed");
   if (b->wide) {

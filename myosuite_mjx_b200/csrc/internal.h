@@ -48,6 +48,10 @@ struct myo_batch {
   int nworld;
   int slot;      // constant-memory parameter slot
   const TeamVariant* kern;   // step kernel variant (lanes per world) chosen for this batch size
+  // the build that runs launches of three or more fused substeps: two co-resident CTAs drift into different phases over
+  // the substeps and lose the shared instruction stream (16384 worlds x 10 substeps: 27.1 ms for one CTA per SM in two
+  // waves, 31.4 ms for two co-resident CTAs; one substep: 2.06 against 1.82 ms, profiles/r1zz_fused_variants.txt)
+  const TeamVariant* kern_fused = nullptr;
   bool dirty;    // parameters changed since the last upload
   bool wide;     // some wide output field is bound: the output kernel runs after the step kernel
   // myo_step_host: the state is final when the step kernel ends, so its device-to-host copies run on a side stream

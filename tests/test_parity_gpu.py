@@ -273,6 +273,31 @@ def test_two_ctas_per_sm_variant_equals_one(models, monkeypatch):
         assert got == want
 
 
+def test_large_batch_fused_substeps_switch_builds(models):
+    """Above 8288 worlds a launch of one or two substeps runs the two-CTAs-per-SM build, a launch of three or more the
+    one-CTA build (co-resident CTAs drift apart over fused substeps); both are the same source, so the states agree bit for bit."""
+    import gc
+    import torch
+    from myosuite_mjx_b200 import mjx
+    m = models("hand")
+    nw = 8320
+    qpos, qvel, act, ctrl = parity.random_state(m, nw, 9, qpos_spread=0.6)
+    model = mjx.put_model(m)
+    a = mjx.put_data(model, dict(qpos=qpos, qvel=qvel, act=act, ctrl=ctrl), nworld=nw, fields="core")
+    assert (a.team, a.ctas_per_sm) == (8, 2)
+    mjx.step(model, a, 4)
+    torch.cuda.synchronize()
+    ref = {f: getattr(a, f).clone() for f in ("qpos", "qvel", "act", "qacc_warmstart")}
+    del a; gc.collect()
+    b = mjx.put_data(model, dict(qpos=qpos, qvel=qvel, act=act, ctrl=ctrl), nworld=nw, fields="core")
+    for _ in range(4):
+        mjx.step(model, b, 1)
+    torch.cuda.synchronize()
+    for f, v in ref.items():
+        assert torch.equal(getattr(b, f), v), f"{f}: fused launch (one CTA per SM) differs from single-step launches (two CTAs per SM)"
+    del b; gc.collect()
+
+
 def test_deterministic_and_output_mask_invariant(models):
     """Bitwise-identical state whether all of mjData or only the core fields are materialised, run twice."""
     import torch
