@@ -226,6 +226,16 @@ int myo_forward_posvel(myo_batch *b, const int32_t *world_mask_dev, void *cuda_s
  * Output fields describe the last substep's forward pass, as mjData does after mj_step. */
 int myo_step(myo_batch *b, int nsubsteps, void *cuda_stream);
 
+/* Pipelined wide outputs (opt-in, for rollouts that do not read the full mjData after every step): with `on`, the
+ * wide-output kernel of a full unmasked myo_step / myo_step_host (site / geom / body poses, dense ten_J, actuator_moment,
+ * qM, efc_J, contact_* ..., see csrc/out.cu) is enqueued on a library-owned side stream and runs under the NEXT step's
+ * kernel (the step alternates between two scratch buffers).  State fields and every field the step kernel writes itself
+ * keep the caller's stream order; the wide fields of the last step are complete on `cuda_stream` after
+ * myo_outputs_join, which every other entry point (forward, reset, masked / posvel passes, env steps) calls itself.
+ * Off (the default): mjx.step semantics, every field is complete in stream order when myo_step returns. */
+int myo_batch_set_pipelined(myo_batch *b, int on);
+int myo_outputs_join(myo_batch *b, void *cuda_stream);
+
 /* mj_resetData + mj_forward on worlds whose mask entry is non-zero (NULL = all): qpos=qpos0, qvel=act=0,
  * time=0, warmstart=0, status=0 (reference: myosuite/robot/robot.py:976-979). world_mask is int32[nworld] on device. */
 int myo_reset(myo_batch *b, const int32_t *world_mask_dev, void *cuda_stream);

@@ -162,7 +162,7 @@ int myo_batch_create(const myo_model* m, int nworld, int nconmax, int njmax, myo
     if (b->kern->ctas_per_sm > 1 && !getenv("MYO_CTAS"))
       for (const TeamVariant& v : kVariants) if (v.team == b->kern->team && v.ctas_per_sm == 1) b->kern_fused = &v;   // same scratch layout
     if (cudaMalloc(&p, b->kern->scratch_floats(b->L, nworld) * sizeof(float)) != cudaSuccess) { g_slot_used[b->slot] = false; delete b; return fail(MYO_ERR_CUDA, "cudaMalloc of the per-world scratch failed"); }
-    b->owned.push_back(p); b->scratch = (float*)p;
+    b->owned.push_back(p); b->scratch = (float*)p; b->scratch_buf[0] = b->scratch;
   }
   // library-owned default state buffers (bind overrides them)
   for (int f : kStateFields) {
@@ -178,7 +178,8 @@ void myo_batch_destroy(myo_batch* b) {
   if (!b) return;
   cudaSetDevice(b->model->device);
   for (void* p : b->owned) cudaFree(p);
-  if (b->copy_stream) { cudaStreamDestroy((cudaStream_t)b->copy_stream); cudaEventDestroy((cudaEvent_t)b->ev_step); cudaEventDestroy((cudaEvent_t)b->ev_copy); }
+  for (int i = 0; i < 2; i++) if (b->ev_out[i]) { cudaEventSynchronize((cudaEvent_t)b->ev_out[i]); cudaEventDestroy((cudaEvent_t)b->ev_out[i]); }
+  if (b->copy_stream) { cudaStreamSynchronize((cudaStream_t)b->copy_stream); cudaStreamDestroy((cudaStream_t)b->copy_stream); cudaEventDestroy((cudaEvent_t)b->ev_step); cudaEventDestroy((cudaEvent_t)b->ev_copy); }
   if (b->slot >= 0) g_slot_used[b->slot] = false;
   delete b;
 }
@@ -199,8 +200,26 @@ int myo_batch_bind(myo_batch* b, int field, void* dev_ptr, int64_t nbytes) {
   } else {
     for (int f : kStateFields) if (f == field) return fail(MYO_ERR_ARG, "state fields cannot be unbound");
   }
+  if (b->out_pending) { cudaEventSynchronize((cudaEvent_t)b->ev_out[b->cur]); b->out_pending = false; }   // a running output kernel still writes the old buffers
   b->F.p[field] = dev_ptr;
   b->dirty = true;
+  return MYO_OK;
+}
+
+static int ensureSide(myo_batch* b) {
+  if (b->copy_stream) return MYO_OK;
+  cudaStream_t cs; cudaEvent_t e0, e1;
+  if (cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking) != cudaSuccess || cudaEventCreateWithFlags(&e0, cudaEventDisableTiming) != cudaSuccess ||
+      cudaEventCreateWithFlags(&e1, cudaEventDisableTiming) != cudaSuccess)
+    return fail(MYO_ERR_CUDA, "side stream creation failed");
+  b->copy_stream = cs; b->ev_step = e0; b->ev_copy = e1;
+  return MYO_OK;
+}
+// the caller's stream waits for a pipelined output kernel that may still be running
+static int joinOutputs(myo_batch* b, void* stream) {
+  if (!b->out_pending) return MYO_OK;
+  if (cudaStreamWaitEvent((cudaStream_t)stream, (cudaEvent_t)b->ev_out[b->cur], 0) != cudaSuccess) return fail(MYO_ERR_CUDA, "joining the output kernel failed");
+  b->out_pending = false;
   return MYO_OK;
 }
 
@@ -232,17 +251,55 @@ static int launch(myo_batch* b, int nsub, int forward_only, const int32_t* mask,
     }
     b->dirty = false;
   }
+  // A full, unmasked step of a pipelined batch with wide outputs: its output kernel goes to the side stream and the step
+  // runs on the other scratch buffer, so the NEXT step's kernel does not wait for it.  Every other launch joins first
+  // and works on the buffer of the last pass (posvel / masked passes read what that pass left).
+  const bool pipe = b->pipelined && b->wide && !forward_only && !mask && !do_reset;
+  if (pipe) {
+    const int nxt = b->cur ^ 1;
+    if ((rc = ensureSide(b)) != MYO_OK) return rc;
+    if (!b->scratch_buf[nxt]) {
+      void* p = nullptr;
+      if (cudaMalloc(&p, b->kern->scratch_floats(b->L, b->nworld) * sizeof(float)) != cudaSuccess) return fail(MYO_ERR_CUDA, "cudaMalloc of the second scratch buffer failed");
+      b->owned.push_back(p); b->scratch_buf[nxt] = (float*)p;
+    }
+    for (int i = 0; i < 2; i++)
+      if (!b->ev_out[i]) { cudaEvent_t e; if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess) return fail(MYO_ERR_CUDA, "event creation failed"); b->ev_out[i] = e; }
+    // the output kernel that last read buffer `nxt` (two steps ago) must be done before this step overwrites it
+    if (b->ev_out_set[nxt] && cudaStreamWaitEvent((cudaStream_t)stream, (cudaEvent_t)b->ev_out[nxt], 0) != cudaSuccess) return fail(MYO_ERR_CUDA, "stream wait failed");
+    b->cur = nxt;
+  } else if ((rc = joinOutputs(b, stream)) != MYO_OK) return rc;
+  b->scratch = b->scratch_buf[b->cur];
   g_launches++;
   const TeamVariant* kern = (!forward_only && nsub >= 3) ? b->kern_fused : b->kern;
   if (kern->launch(b->slot, b->L, b->nworld, nsub, forward_only, mask, do_reset, b->scratch, stream) != 0)
     return fail(MYO_ERR_CUDA, std::string("kernel launch failed: ") + cudaGetErrorString(cudaGetLastError()));
+  if (pipe) after_step = (cudaEvent_t)b->ev_step;
   if (after_step && cudaEventRecord(after_step, (cudaStream_t)stream) != cudaSuccess) return fail(MYO_ERR_CUDA, "event record failed");
   if (b->wide) {
     g_launches++;
-    if (myo_out_launch(b->slot, b->nworld, 32 / b->kern->team, mask, forward_only == 2, b->scratch, stream) != 0)
+    cudaStream_t os = (cudaStream_t)stream;
+    if (pipe) {
+      os = (cudaStream_t)b->copy_stream;
+      if (cudaStreamWaitEvent(os, (cudaEvent_t)b->ev_step, 0) != cudaSuccess) return fail(MYO_ERR_CUDA, "stream wait failed");
+    }
+    if (myo_out_launch(b->slot, b->nworld, 32 / b->kern->team, mask, forward_only == 2, b->scratch, os) != 0)
       return fail(MYO_ERR_CUDA, std::string("kernel launch failed: ") + cudaGetErrorString(cudaGetLastError()));
+    if (pipe) {
+      if (cudaEventRecord((cudaEvent_t)b->ev_out[b->cur], os) != cudaSuccess) return fail(MYO_ERR_CUDA, "event record failed");
+      b->ev_out_set[b->cur] = true; b->out_pending = true;
+    }
   }
   return MYO_OK;
+}
+int myo_batch_set_pipelined(myo_batch* b, int on) {
+  if (!b) return fail(MYO_ERR_ARG, "null batch");
+  b->pipelined = on != 0;
+  return MYO_OK;
+}
+int myo_outputs_join(myo_batch* b, void* stream) {
+  if (!b) return fail(MYO_ERR_ARG, "null batch");
+  return joinOutputs(b, stream);
 }
 int myo_forward(myo_batch* b, void* stream) { return launch(b, 0, 1, nullptr, 0, stream); }
 int myo_step(myo_batch* b, int nsubsteps, void* stream) {
@@ -271,13 +328,8 @@ int myo_step_host(myo_batch* b, int nsubsteps, const float* qpos, const float* q
   // that waits for the step kernel only and run under the wide-output kernel; the caller's stream joins before returning.
   bool fork = false;
   for (int i = 0; i < kNumWideOutFields; i++) fork |= b->F.p[kWideOutFields[i]] != nullptr;
-  if (fork && !b->copy_stream) {
-    cudaStream_t cs; cudaEvent_t e0, e1;
-    if (cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking) != cudaSuccess || cudaEventCreateWithFlags(&e0, cudaEventDisableTiming) != cudaSuccess ||
-        cudaEventCreateWithFlags(&e1, cudaEventDisableTiming) != cudaSuccess)
-      return fail(MYO_ERR_CUDA, "side stream creation failed");
-    b->copy_stream = cs; b->ev_step = e0; b->ev_copy = e1;
-  }
+  if (b->pipelined) fork = false;   // the output kernel itself leaves the caller's stream: the copies follow the step kernel there
+  if (fork && (rc = ensureSide(b)) != MYO_OK) return rc;
   rc = launch(b, nsubsteps, 0, nullptr, 0, stream, fork ? (cudaEvent_t)b->ev_step : nullptr);
   if (rc) return rc;
   cudaStream_t cs = fork ? (cudaStream_t)b->copy_stream : s;

@@ -59,6 +59,15 @@ struct myo_batch {
   void* copy_stream = nullptr; void* ev_step = nullptr; void* ev_copy = nullptr;
   void* wrap_cleared[2] = {nullptr, nullptr};   // wrap_obj / wrap_xpos buffers already zeroed once (api.cu launch)
   float* scratch; // per-world intermediates, [nwarps][L.total][worlds per warp]
+  // Pipelined outputs (myo_batch_set_pipelined): the wide-output kernel of step k runs on the side stream under the step
+  // kernel of step k+1.  Two scratch buffers alternate; `cur` holds the last pass; ev_out[i] marks the end of the last
+  // output kernel that read buffer i; `out_pending`: an output kernel may still be running (joined by the next call that
+  // is not itself a pipelined step, or by myo_outputs_join).
+  float* scratch_buf[2] = {nullptr, nullptr};
+  void* ev_out[2] = {nullptr, nullptr};
+  bool ev_out_set[2] = {false, false};
+  int cur = 0;
+  bool pipelined = false, out_pending = false;
   std::vector<void*> owned;
 };
 

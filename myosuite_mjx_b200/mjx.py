@@ -110,10 +110,25 @@ class Data:
         _lib.check(_lib.lib().myo_batch_bind(self._h, fid, ctypes.c_void_p(tensor.data_ptr()), tensor.numel() * tensor.element_size()))
         self._t[name.lower()] = tensor
 
+    def set_pipelined(self, on=True):
+        """Opt in to pipelined wide outputs (include/myostep.h, myo_batch_set_pipelined): the wide-output kernel of a step
+        runs under the next step's kernel.  Reading a field through this object joins it first, so values read here are
+        always complete; tensors fetched earlier and kept by the caller are only complete after `join()`."""
+        if not on:
+            self.join()
+        _lib.check(_lib.lib().myo_batch_set_pipelined(self._h, 1 if on else 0))
+        self.__dict__["_pipelined"] = bool(on)
+        return self
+
+    def join(self):
+        if self.__dict__.get("_pipelined"):
+            _lib.check(_lib.lib().myo_outputs_join(self._h, _stream()))
+
     def __getattr__(self, name):
         t = self.__dict__.get("_t", {})
         key = {"q": "qpos", "qd": "qvel"}.get(name, name.lower())   # brax State aliases (myodm_v0.py:201-202)
         if key in t:
+            self.join()
             return self._view(key, t[key])
         raise AttributeError(name)
 
@@ -130,6 +145,7 @@ class Data:
 
     def storage(self, name):
         """the bound `[k, nworld]` buffer itself"""
+        self.join()
         return self._t[name.lower()]
 
     def fields(self):

@@ -298,6 +298,38 @@ def test_large_batch_fused_substeps_switch_builds(models):
     del b; gc.collect()
 
 
+def test_pipelined_outputs_equal_stream_ordered(models):
+    """myo_batch_set_pipelined: the wide-output kernel of step k runs on a side stream under step k+1 (two scratch buffers);
+    after the join every field equals the stream-ordered default bit for bit, also across masked / posvel passes and resets."""
+    import gc
+    import torch
+    from myosuite_mjx_b200 import mjx
+    m = models("hand")
+    nw = 256
+    qpos, qvel, act, ctrl = parity.random_state(m, nw, 13, qpos_spread=0.9)
+    model = mjx.put_model(m)
+    mask = torch.zeros(nw, dtype=torch.int32, device="cuda"); mask[::3] = 1
+    snaps = []
+    for pipelined in (False, True):
+        d = mjx.put_data(model, dict(qpos=qpos, qvel=qvel, act=act, ctrl=ctrl), nworld=nw, fields="all")
+        if pipelined:
+            d.set_pipelined(True)
+        snap = []
+        for _ in range(5):
+            mjx.step(model, d, 1)
+        snap.append({f: getattr(d, f).clone() for f in d.fields()})        # field access joins
+        mjx.step(model, d, 1); mjx.refresh(model, d, mask)                   # posvel pass reads what the last full pass left
+        snap.append({f: getattr(d, f).clone() for f in d.fields()})
+        mjx.step(model, d, 2); mjx.reset(model, d, mask); mjx.step(model, d, 1); mjx.step(model, d, 1)
+        snap.append({f: getattr(d, f).clone() for f in d.fields()})
+        torch.cuda.synchronize()
+        snaps.append(snap)
+        del d; gc.collect()
+    for a, b in zip(*snaps):
+        for f in a:
+            assert torch.equal(a[f], b[f]), f"{f}: pipelined outputs differ"
+
+
 def test_deterministic_and_output_mask_invariant(models):
     """Bitwise-identical state whether all of mjData or only the core fields are materialised, run twice."""
     import torch
