@@ -192,8 +192,9 @@ void myo_batch_destroy(myo_batch *b);
 int myo_batch_nconmax(const myo_batch *b);
 int myo_batch_njmax(const myo_batch *b);
 int myo_batch_smem_bytes(const myo_batch *b);   /* bytes of per-world scratch in the library-owned global buffer */
-int myo_batch_team(const myo_batch *b);         /* lanes per world of the kernel variant picked for this batch size (1..16) */
-int myo_batch_ctas_per_sm(const myo_batch *b);  /* co-resident step-kernel CTAs per SM of that variant (2 above 8288 worlds) */
+int myo_batch_team(const myo_batch *b);         /* lanes per world of the TEAM-mode kernels (constraint rows, Newton) picked for this batch (4, 8 or 16) */
+int myo_batch_ctas_per_sm(const myo_batch *b);  /* always 1 (kept for ABI stability: round 1 had a two-CTAs-per-SM build of the one-launch kernel) */
+int myo_batch_engine(const myo_batch *b);       /* 1: phase pipeline (lane = world kernels + team solver, the default); 0: one-launch kernel (MYO_ENGINE=mono) */
 
 /* Per-world element count / element size of a field for this batch (0 elements = field absent for the model). */
 int64_t myo_field_count(const myo_batch *b, int field);

@@ -13,27 +13,21 @@
 
 
 namespace {
-const TeamVariant kVariants[] = {
-    {1, 1, myo_team_upload_1, myo_team_launch_1, myo_team_scratch_1}, {2, 1, myo_team_upload_2, myo_team_launch_2, myo_team_scratch_2},
-    {4, 1, myo_team_upload_4, myo_team_launch_4, myo_team_scratch_4}, {8, 1, myo_team_upload_8, myo_team_launch_8, myo_team_scratch_8},
-    {16, 1, myo_team_upload_16, myo_team_launch_16, myo_team_scratch_16},
-    {8, 2, myo_team_upload_8x2, myo_team_launch_8x2, myo_team_scratch_8x2}};
+const TeamVariant kVariants[] = {{4, myo_team_upload_4, myo_team_launch_4, myo_team_solve_4},
+                                 {8, myo_team_upload_8, myo_team_launch_8, myo_team_solve_8},
+                                 {16, myo_team_upload_16, myo_team_launch_16, myo_team_solve_16}};
 int64_t g_launches = 0;
-// lanes per world: the step is latency-bound, so small batches get wider teams (more warps per SM).  Up to 8288 worlds:
-// the widest team whose warps are all resident at once in one 14-warp CTA per SM (148 SMs, <= 128 registers).  Above
-// that: 8 lanes per world with TWO co-resident CTAs per SM (<= 72 registers): the second CTA fills the first one's phase
-// barriers and load stalls (profiles/r1v_nworld_sweep.txt: 16384 worlds 2.03 ms/step against 2.28 for two waves of the
-// one-CTA build and 2.63 for 4 lanes per world).
-const TeamVariant* pickVariant(int nworld) {
-  const int64_t resident = (int64_t)148 * 14 * 32;
-  int team = 16, ctas = 1;
-  while (team > 8 && (int64_t)nworld * team > resident) team >>= 1;
-  if ((int64_t)nworld * team > resident) ctas = 2;
-  if (const char* e = getenv("MYO_TEAM")) { team = atoi(e); ctas = 1; }   // developer knobs
-  if (const char* e = getenv("MYO_CTAS")) ctas = atoi(e);
-  for (const TeamVariant& v : kVariants) if (v.team == team && v.ctas_per_sm == ctas) return &v;
+// Engine: the phase pipeline (tile.cu lane = world kernels + team.cu solveKernel) unless MYO_ENGINE=mono asks for the
+// round-1 whole-step kernel.  Lanes per world of the TEAM-mode kernels: 8 (the solver's loops -- ~65 rows, 23 dofs, ~13
+// contacts per MyoHand world -- keep 8 lanes busy; 16 lanes idle half of them); the one-launch kernel takes 16 when all of
+// its warps are resident at once (small batches).  MYO_TEAM overrides (developer knob).
+bool pickMono() { const char* e = getenv("MYO_ENGINE"); return e && std::string(e) == "mono"; }
+const TeamVariant* pickVariant(int nworld, bool mono) {
+  int team = 8;
+  if (mono && (int64_t)nworld * 16 <= (int64_t)148 * 14 * 32) team = 16;
+  if (const char* e = getenv("MYO_TEAM")) team = atoi(e);
   for (const TeamVariant& v : kVariants) if (v.team == team) return &v;
-  return &kVariants[3];
+  return &kVariants[1];
 }
 thread_local std::string g_err;
 bool g_slot_used[64] = {false};
@@ -157,11 +151,14 @@ int myo_batch_create(const myo_model* m, int nworld, int nconmax, int njmax, myo
   } catch (const std::string& e) { g_slot_used[b->slot] = false; delete b; return fail(MYO_ERR_ARG, e); }
   {
     void* p = nullptr;
-    b->kern = pickVariant(nworld);
-    b->kern_fused = b->kern;
-    if (b->kern->ctas_per_sm > 1 && !getenv("MYO_CTAS"))
-      for (const TeamVariant& v : kVariants) if (v.team == b->kern->team && v.ctas_per_sm == 1) b->kern_fused = &v;   // same scratch layout
-    if (cudaMalloc(&p, b->kern->scratch_floats(b->L, nworld) * sizeof(float)) != cudaSuccess) { g_slot_used[b->slot] = false; delete b; return fail(MYO_ERR_CUDA, "cudaMalloc of the per-world scratch failed"); }
+    b->mono = pickMono();
+    b->kern = pickVariant(nworld, b->mono);
+    b->stride = (nworld + 31) & ~31;
+    // scratch element k of world w lives at k * stride + w: the kernels form that index in 32 bits
+    if ((int64_t)b->L.total * b->stride >= ((int64_t)1 << 31)) { g_slot_used[b->slot] = false; delete b; return fail(MYO_ERR_ARG, "batch too large: per-world scratch x worlds exceeds 2^31 floats"); }
+    const size_t bytes = (size_t)b->L.total * b->stride * sizeof(float);
+    // zeroed once: a record the kernels have not written yet (rows past an overflow, lanes of a partial tile) reads as zeros
+    if (cudaMalloc(&p, bytes) != cudaSuccess || cudaMemset(p, 0, bytes) != cudaSuccess) { g_slot_used[b->slot] = false; delete b; return fail(MYO_ERR_CUDA, "cudaMalloc of the per-world scratch failed"); }
     b->owned.push_back(p); b->scratch = (float*)p; b->scratch_buf[0] = b->scratch;
   }
   // library-owned default state buffers (bind overrides them)
@@ -187,7 +184,8 @@ int myo_batch_nconmax(const myo_batch* b) { return b ? b->D.nconmax : 0; }
 int myo_batch_njmax(const myo_batch* b) { return b ? b->D.njmax : 0; }
 int myo_batch_smem_bytes(const myo_batch* b) { return b ? b->L.total * 4 : 0; }
 int myo_batch_team(const myo_batch* b) { return b ? b->kern->team : 0; }
-int myo_batch_ctas_per_sm(const myo_batch* b) { return b ? b->kern->ctas_per_sm : 0; }
+int myo_batch_ctas_per_sm(const myo_batch* b) { return b ? 1 : 0; }
+int myo_batch_engine(const myo_batch* b) { return b ? (b->mono ? 0 : 1) : -1; }
 int64_t myo_field_count(const myo_batch* b, int field) { return (b && field >= 0 && field < MYO_F_COUNT) ? fieldCount(b->D, field) : 0; }
 
 int myo_batch_bind(myo_batch* b, int field, void* dev_ptr, int64_t nbytes) {
@@ -200,6 +198,7 @@ int myo_batch_bind(myo_batch* b, int field, void* dev_ptr, int64_t nbytes) {
   } else {
     for (int f : kStateFields) if (f == field) return fail(MYO_ERR_ARG, "state fields cannot be unbound");
   }
+  if (b->F.p[field] == dev_ptr) return MYO_OK;   // re-binding the same buffer (a caller that binds on every call) changes nothing
   if (b->out_pending) { cudaEventSynchronize((cudaEvent_t)b->ev_out[b->cur]); b->out_pending = false; }   // a running output kernel still writes the old buffers
   b->F.p[field] = dev_ptr;
   b->dirty = true;
@@ -223,9 +222,75 @@ static int joinOutputs(myo_batch* b, void* stream) {
   return MYO_OK;
 }
 
+// Path-point buffers: the kernels clear only the entries a wrap state can reach; the rest of a newly bound buffer is
+// zeroed here once (mj_makeData's zeros), on the caller's stream.
+static int clearPathPoints(myo_batch* b, void* stream) {
+  const int wf[2] = {MYO_F_WRAP_OBJ, MYO_F_WRAP_XPOS};
+  for (int i = 0; i < 2; i++) {
+    void* p = b->F.p[wf[i]];
+    if (!p || p == b->wrap_cleared[i]) continue;
+    if (cudaMemsetAsync(p, 0, (size_t)b->nworld * fieldCount(b->D, wf[i]) * 4, (cudaStream_t)stream) != cudaSuccess)
+      return fail(MYO_ERR_CUDA, "clearing the path-point buffers failed");
+    b->wrap_cleared[i] = p;
+  }
+  return MYO_OK;
+}
+
+// The phase pipeline: one mj_step = kin -> tendon -> inertia -> collide -> velact (tile.cu, lane = world) -> solve (team.cu,
+// 8 lanes per world) -> conout -> finish (tile.cu).  All launches go to the caller's stream, in order; every mjData field
+// is written by the phase that produces it, as full lines; inner substeps of a fused launch materialise nothing.
+static int launchPhases(myo_batch* b, int nsub, int forward_only, const int32_t* mask, int do_reset, void* stream) {
+  int rc;
+  if (b->dirty) {
+    if (myo_tile_upload(b->slot, b->D, b->L, b->F, stream) != 0 || b->kern->upload(b->slot, b->D, b->L, b->F, stream) != 0)
+      return fail(MYO_ERR_CUDA, "parameter upload failed");
+    static const int conFields[] = {MYO_F_NCON, MYO_F_NEFC, MYO_F_SOLVER_NITER, MYO_F_CONTACT_GEOM, MYO_F_CONTACT_DIM, MYO_F_CONTACT_EFC_ADDRESS,
+                                    MYO_F_CONTACT_DIST, MYO_F_CONTACT_POS, MYO_F_CONTACT_FRAME, MYO_F_CONTACT_INCLUDEMARGIN, MYO_F_CONTACT_FRICTION,
+                                    MYO_F_CONTACT_SOLREF, MYO_F_CONTACT_SOLIMP, MYO_F_EFC_J, MYO_F_EFC_POS, MYO_F_EFC_MARGIN, MYO_F_EFC_D,
+                                    MYO_F_EFC_AREF, MYO_F_EFC_FORCE, MYO_F_EFC_TYPE};
+    b->wide = false;   // here: some contact / constraint record field is bound, conoutKernel runs
+    for (int f : conFields) b->wide |= b->F.p[f] != nullptr;
+    if ((rc = clearPathPoints(b, stream)) != MYO_OK) return rc;
+    b->dirty = false;
+  }
+  const bool posvel = forward_only == 2;
+  const int nloop = forward_only ? 1 : nsub;
+  const int slot = b->slot, nw = b->nworld, st = b->stride;
+  float* scr = b->scratch;
+  auto tile = [&](int k, int fslot, int flags) {
+    g_launches++;
+    return myo_tile_launch(k, slot, fslot, nw, st, mask, flags, scr, stream);
+  };
+  bool ok = true;
+  for (int sub = 0; sub < nloop && ok; sub++) {
+    const bool first = sub == 0, last = sub == nloop - 1;
+    const int fslot = last ? slot : MYO_PARAM_SLOTS;   // slot MYO_PARAM_SLOTS: no field bound, "materialise nothing"
+    ok &= tile(MYO_K_KIN, fslot, (first ? (do_reset ? MYO_KIN_RESET : MYO_KIN_LOAD) : 0) | (forward_only ? 0 : MYO_KIN_CHECK)) == 0;
+    ok &= tile(MYO_K_TENDON, fslot, 0) == 0;
+    if (!posvel) {
+      ok &= tile(MYO_K_INERTIA, fslot, forward_only ? 0 : 1) == 0;
+      ok &= tile(MYO_K_COLLIDE, fslot, 0) == 0;
+    }
+    ok &= tile(MYO_K_VELACT, fslot, posvel ? 1 : 0) == 0;
+    if (posvel) break;
+    g_launches++;
+    ok &= b->kern->solve(slot, fslot, b->L, nw, st, mask, forward_only ? 0 : 1, scr, stream) == 0;
+    if (last && b->wide) ok &= tile(MYO_K_CONOUT, fslot, 0) == 0;
+    ok &= tile(MYO_K_FINISH, fslot, (forward_only ? 0 : MYO_FIN_EULER) | (last && (!forward_only || do_reset) ? MYO_FIN_STATE : 0) |
+                                        (last ? MYO_FIN_WARM | MYO_FIN_ACC : 0)) == 0;
+  }
+  if (!ok) return fail(MYO_ERR_CUDA, std::string("kernel launch failed: ") + cudaGetErrorString(cudaGetLastError()));
+  return MYO_OK;
+}
+
 static int launch(myo_batch* b, int nsub, int forward_only, const int32_t* mask, int do_reset, void* stream, cudaEvent_t after_step = nullptr) {
   int rc = checkReady(b);
   if (rc) return rc;
+  if (!b->mono) {
+    if ((rc = launchPhases(b, nsub, forward_only, mask, do_reset, stream)) != MYO_OK) return rc;
+    if (after_step && cudaEventRecord(after_step, (cudaStream_t)stream) != cudaSuccess) return fail(MYO_ERR_CUDA, "event record failed");
+    return MYO_OK;
+  }
   if (b->dirty) {
     // wide outputs (out.cu) are written by the second kernel; the step kernel sees null pointers for them
     static const bool wide_on = !(getenv("MYO_WIDE_OUT") && atoi(getenv("MYO_WIDE_OUT")) == 0);
@@ -237,18 +302,8 @@ static int launch(myo_batch* b, int nsub, int forward_only, const int32_t* mask,
     SmemLayout Ls = b->L;
     Ls.wantw = b->F.p[MYO_F_WRAP_XPOS] || b->F.p[MYO_F_WRAP_OBJ] || b->F.p[MYO_F_TEN_WRAPADR] || b->F.p[MYO_F_TEN_WRAPNUM];
     if (b->kern->upload(b->slot, b->D, Ls, Fstep, stream) != 0) return fail(MYO_ERR_CUDA, "parameter upload failed");
-    if (b->kern_fused != b->kern && b->kern_fused->upload(b->slot, b->D, Ls, Fstep, stream) != 0) return fail(MYO_ERR_CUDA, "parameter upload failed");
     if (b->wide && myo_out_upload(b->slot, b->D, b->L, b->F, stream) != 0) return fail(MYO_ERR_CUDA, "parameter upload failed");
-    // Path-point buffers: the kernel clears only the entries a wrap state can reach; the rest of a newly bound buffer is
-    // zeroed here once (mj_makeData's zeros), on the caller's stream.
-    const int wf[2] = {MYO_F_WRAP_OBJ, MYO_F_WRAP_XPOS};
-    for (int i = 0; i < 2; i++) {
-      void* p = b->F.p[wf[i]];
-      if (!p || p == b->wrap_cleared[i]) continue;
-      if (cudaMemsetAsync(p, 0, (size_t)b->nworld * fieldCount(b->D, wf[i]) * 4, (cudaStream_t)stream) != cudaSuccess)
-        return fail(MYO_ERR_CUDA, "clearing the path-point buffers failed");
-      b->wrap_cleared[i] = p;
-    }
+    if ((rc = clearPathPoints(b, stream)) != MYO_OK) return rc;
     b->dirty = false;
   }
   // A full, unmasked step of a pipelined batch with wide outputs: its output kernel goes to the side stream and the step
@@ -260,7 +315,8 @@ static int launch(myo_batch* b, int nsub, int forward_only, const int32_t* mask,
     if ((rc = ensureSide(b)) != MYO_OK) return rc;
     if (!b->scratch_buf[nxt]) {
       void* p = nullptr;
-      if (cudaMalloc(&p, b->kern->scratch_floats(b->L, b->nworld) * sizeof(float)) != cudaSuccess) return fail(MYO_ERR_CUDA, "cudaMalloc of the second scratch buffer failed");
+      const size_t bytes = (size_t)b->L.total * b->stride * sizeof(float);
+      if (cudaMalloc(&p, bytes) != cudaSuccess || cudaMemset(p, 0, bytes) != cudaSuccess) return fail(MYO_ERR_CUDA, "cudaMalloc of the second scratch buffer failed");
       b->owned.push_back(p); b->scratch_buf[nxt] = (float*)p;
     }
     for (int i = 0; i < 2; i++)
@@ -271,8 +327,7 @@ static int launch(myo_batch* b, int nsub, int forward_only, const int32_t* mask,
   } else if ((rc = joinOutputs(b, stream)) != MYO_OK) return rc;
   b->scratch = b->scratch_buf[b->cur];
   g_launches++;
-  const TeamVariant* kern = (!forward_only && nsub >= 3) ? b->kern_fused : b->kern;
-  if (kern->launch(b->slot, b->L, b->nworld, nsub, forward_only, mask, do_reset, b->scratch, stream) != 0)
+  if (b->kern->launch(b->slot, b->L, b->nworld, b->stride, nsub, forward_only, mask, do_reset, b->scratch, stream) != 0)
     return fail(MYO_ERR_CUDA, std::string("kernel launch failed: ") + cudaGetErrorString(cudaGetLastError()));
   if (pipe) after_step = (cudaEvent_t)b->ev_step;
   if (after_step && cudaEventRecord(after_step, (cudaStream_t)stream) != cudaSuccess) return fail(MYO_ERR_CUDA, "event record failed");
@@ -283,7 +338,7 @@ static int launch(myo_batch* b, int nsub, int forward_only, const int32_t* mask,
       os = (cudaStream_t)b->copy_stream;
       if (cudaStreamWaitEvent(os, (cudaEvent_t)b->ev_step, 0) != cudaSuccess) return fail(MYO_ERR_CUDA, "stream wait failed");
     }
-    if (myo_out_launch(b->slot, b->nworld, 32 / b->kern->team, mask, forward_only == 2, b->scratch, os) != 0)
+    if (myo_out_launch(b->slot, b->nworld, b->stride, mask, forward_only == 2, b->scratch, os) != 0)
       return fail(MYO_ERR_CUDA, std::string("kernel launch failed: ") + cudaGetErrorString(cudaGetLastError()));
     if (pipe) {
       if (cudaEventRecord((cudaEvent_t)b->ev_out[b->cur], os) != cudaSuccess) return fail(MYO_ERR_CUDA, "event record failed");
@@ -328,7 +383,7 @@ int myo_step_host(myo_batch* b, int nsubsteps, const float* qpos, const float* q
   // that waits for the step kernel only and run under the wide-output kernel; the caller's stream joins before returning.
   bool fork = false;
   for (int i = 0; i < kNumWideOutFields; i++) fork |= b->F.p[kWideOutFields[i]] != nullptr;
-  if (b->pipelined) fork = false;   // the output kernel itself leaves the caller's stream: the copies follow the step kernel there
+  if (b->pipelined || !b->mono) fork = false;   // the output kernel itself leaves the caller's stream: the copies follow the step kernel there
   if (fork && (rc = ensureSide(b)) != MYO_OK) return rc;
   rc = launch(b, nsubsteps, 0, nullptr, 0, stream, fork ? (cudaEvent_t)b->ev_step : nullptr);
   if (rc) return rc;

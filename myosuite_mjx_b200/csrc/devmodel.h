@@ -110,14 +110,15 @@ struct FieldPtrs {
   void *p[MYO_F_COUNT];
 };
 
-// per-world scratch layout (float offsets), computed on the host
+// per-world scratch layout (float offsets into the world's column of the [total][stride] scratch), computed on the host
 struct SmemLayout {
   int total;      // floats per world
   // persistent region
   int qpos, qvel, act, ctrl, frames, xanchor, xaxis, rootcom, cinert, crb, cdof, cdof_dot, cvel, cacc, qM, qLD, qLDinv, qH,
       qHinv, tenlen, tenvel, tenJ, actlen, actvel, actforce, actdot, bias, passive, qfrc_act, smooth, qfrc_con, qacc_smooth,
       qacc, warm, tmpv, tforce;
-  int counts;    // ncon, nefc, solver_niter of the last forward pass (int bits), read by the wide-output kernel
+  int counts;    // ncon, nefc, solver_niter of the last forward pass (int bits)
+  int wstate;    // per-world registers that cross kernel boundaries in the phase pipeline: status (int bits), time, skip flag of mj_checkAcc (int bits)
   // overlay region A (tendon stage)
   int slots, ulen, uwrap, uwpt, gpre, upts, tmpbody;
   // overlay region B (collision / constraint / solver stage)

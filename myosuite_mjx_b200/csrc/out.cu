@@ -25,10 +25,9 @@ namespace {
 enum { ROW_EQ = 0, ROW_LIMJ = 1, ROW_LIMT = 2, ROW_CON = 3 };
 enum { E_D = 0, E_AREF, E_JAR, E_JV, E_FORCE, E_DESC0, E_COEF, E_DESC1, E_POS, E_MARGIN };   // as in team.cu
 
-// STRIDE = worlds that share a warp of the step kernel (32 / team width): a compile-time constant here, so a scratch
-// element's address is the world's base pointer plus an immediate offset
-template <int STRIDE> struct CtxT { const float* sm; size_t w, nw; };
-template <int STRIDE> __device__ __forceinline__ float S(const CtxT<STRIDE>& c, int k) { return c.sm[k * STRIDE]; }
+// the scratch is [SmemLayout.total][stride] with the world axis fastest: lanes = consecutive worlds read full lines
+struct CtxT { const float* sm; size_t w, nw; int stride; };
+__device__ __forceinline__ float S(const CtxT& c, int k) { return c.sm[k * c.stride]; }
 // `n` consecutive elements of a [k][nworld] field, first one at element index k0: pointer stepping, no multiplies
 struct Row {
   float* p; size_t nw;
@@ -43,7 +42,7 @@ struct Row {
 };
 
 // world pose of an object fixed to frame f: p = x_f + R_f lpos, M = R_f lmat
-template <int STRIDE> __device__ __forceinline__ void framePose(const CtxT<STRIDE>& c, const SmemLayout& L, int f, const float* lpos, const float* lmat, float* p, float* M, float* R) {
+__device__ __forceinline__ void framePose(const CtxT& c, const SmemLayout& L, int f, const float* lpos, const float* lmat, float* p, float* M, float* R) {
   const int o = L.frames + 16 * f;
 #pragma unroll
   for (int k = 0; k < 9; k++) R[k] = S(c, o + 7 + k);
@@ -62,14 +61,13 @@ template <int STRIDE> __device__ __forceinline__ void framePose(const CtxT<STRID
 #ifndef OUT_MINBLOCKS
 #define OUT_MINBLOCKS 12
 #endif
-template <int STRIDE>
-__global__ void __launch_bounds__(OUT_THREADS, OUT_MINBLOCKS) outKernel(int slot, int nworld, const int* __restrict__ mask, int posvel,
+__global__ void __launch_bounds__(OUT_THREADS, OUT_MINBLOCKS) outKernel(int slot, int nworld, int STRIDE, const int* __restrict__ mask, int posvel,
                                                  const float* __restrict__ scratch) {
   const DevModel& D = oP[slot].D; const SmemLayout& L = oP[slot].L; const FieldPtrs& F = oP[slot].F;
-  CtxT<STRIDE> c; c.w = (size_t)blockIdx.x * OUT_THREADS + threadIdx.x; c.nw = (size_t)nworld;
+  CtxT c; c.w = (size_t)blockIdx.x * OUT_THREADS + threadIdx.x; c.nw = (size_t)nworld; c.stride = STRIDE;
   if (c.w >= c.nw) return;
   if (mask && !mask[c.w]) return;   // a mask restricts the launch to the flagged worlds
-  c.sm = scratch + (c.w / STRIDE) * (size_t)L.total * STRIDE + (c.w % STRIDE);
+  c.sm = scratch + c.w;
   const int nv = D.nv;
   void* sp = F.p[MYO_F_SITE_XPOS]; void* smt = F.p[MYO_F_SITE_XMAT]; void* gp = F.p[MYO_F_GEOM_XPOS]; void* gm = F.p[MYO_F_GEOM_XMAT];
   void* xpos = F.p[MYO_F_XPOS]; void* xquat = F.p[MYO_F_XQUAT]; void* xmat = F.p[MYO_F_XMAT]; void* xipos = F.p[MYO_F_XIPOS];
@@ -353,13 +351,6 @@ int myo_out_launch(int slot, int nworld, int stride, const int* mask, int posvel
   if (grid.y < 1) grid.y = 1;
   if (grid.y > 512) grid.y = 512;
   cudaStream_t st = (cudaStream_t)stream;
-  switch (stride) {
-    case 32: outKernel<32><<<grid, OUT_THREADS, 0, st>>>(slot, nworld, mask, posvel, scratch); break;
-    case 16: outKernel<16><<<grid, OUT_THREADS, 0, st>>>(slot, nworld, mask, posvel, scratch); break;
-    case 8: outKernel<8><<<grid, OUT_THREADS, 0, st>>>(slot, nworld, mask, posvel, scratch); break;
-    case 4: outKernel<4><<<grid, OUT_THREADS, 0, st>>>(slot, nworld, mask, posvel, scratch); break;
-    case 2: outKernel<2><<<grid, OUT_THREADS, 0, st>>>(slot, nworld, mask, posvel, scratch); break;
-    default: return -1;
-  }
+  outKernel<<<grid, OUT_THREADS, 0, st>>>(slot, nworld, stride, mask, posvel, scratch);
   return cudaPeekAtLastError() == cudaSuccess ? 0 : -1;
 }

@@ -638,7 +638,7 @@ void myo_make_layout(DevModel& D, int nconmax_req, int njmax_req, SmemLayout& L)
   L.actlen = take(D.nu); L.actvel = take(D.nu); L.actforce = take(D.nu); L.actdot = take(D.na);
   L.bias = take(nv); L.passive = take(nv); L.qfrc_act = take(nv); L.smooth = take(nv); L.qfrc_con = take(nv);
   L.qacc_smooth = take(nv); L.qacc = take(nv); L.warm = take(nv); L.tmpv = take(nv); L.tforce = take(D.nten);
-  L.counts = take(4);
+  L.counts = take(4); L.wstate = take(4);
   // path points (persistent: the wide-output kernel reads them after the step): tangent points of the wrapped units and the
   // running count of wrapped geom units
   L.uwpt = take(6 * D.ngunit); L.gpre = take(D.ngunit + 1);

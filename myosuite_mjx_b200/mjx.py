@@ -81,6 +81,7 @@ class Data:
         self.smem_bytes = L.myo_batch_smem_bytes(h)
         self.team = L.myo_batch_team(h)
         self.ctas_per_sm = L.myo_batch_ctas_per_sm(h)
+        self.engine = "phase" if L.myo_batch_engine(h) == 1 else "mono"
         self._t = {}
         dev = torch.device("cuda", model.device)
         if fields == "all":
@@ -158,7 +159,11 @@ class Data:
         h = ctypes.c_void_p()
         _lib.check(L.myo_batch_create(self.model._h, self.nworld, self.nconmax, self.njmax, ctypes.byref(h)))
         d._h, d.nconmax, d.njmax, d._t = h, self.nconmax, self.njmax, {}
-        d.smem_bytes, d.team = self.smem_bytes, self.team
+        self.join()
+        d.smem_bytes, d.team, d.ctas_per_sm = self.smem_bytes, L.myo_batch_team(h), 1
+        d.engine = "phase" if L.myo_batch_engine(h) == 1 else "mono"
+        if self.__dict__.get("_pipelined"):
+            d.set_pipelined(True)
         for k, v in self._t.items():
             d.bind(k, v.clone())
         return d

@@ -1,0 +1,182 @@
+"""Every mjData field the product writes, compared with the CPU oracle BY VALUE (VERDICT r1 'what's weak' 2-3, ADVICE).
+
+* constraint rows `[:nefc]`: efc_type exact; efc_J / efc_pos / efc_margin / efc_D / efc_aref to 1e-4 of the field's scale over
+  the batch (efc_D per element, it spans decades); efc_force and qfrc_constraint follow the Newton solve (2e-3, as qacc);
+* contacts `[:ncon]`: contact_dim, contact_efc_address exact; includemargin / friction / solref / solimp 1e-6;
+* qLD (dense lower triangle of the L^T D L factor) 1e-4;
+* padding past nefc / ncon: zeros (efc_type, contact_geom, contact_efc_address: -1), as include/myostep.h states;
+* the BENCHMARKED shape (8192 worlds, default kernel selection): 64 sampled worlds against the oracle after a forward
+  pass, one step and ten steps.
+Oracle = in-repo restatement of MuJoCo 3.2.8 semantics (PARITY UNPINNED)."""
+import numpy as np
+import pytest
+
+import parity
+
+pytestmark = pytest.mark.gpu
+
+MODELS = ["elbow", "finger", "hand", "hand_pose", "hand_sar", "legs"]
+ROW_FIELDS = ["efc_pos", "efc_margin", "efc_D", "efc_aref", "efc_force"]
+CON_FLOAT = {"contact_includemargin": 1, "contact_friction": 5, "contact_solref": 2, "contact_solimp": 5}
+
+
+def oracle_rows(m, qpos, qvel, act, ctrl, warm=None):
+    import oracle
+    o = oracle.Oracle(m)
+    out = []
+    for w in range(qpos.shape[0]):
+        o.set_state(qpos[w], qvel[w], act[w], ctrl[w], warm[w] if warm is not None else np.zeros(m.nv))
+        o.forward()
+        rec = {k: np.array(o.field(k)) for k in ["efc_J", "efc_type", "contact_dim", "contact_efc_address", "contact_geom", "qLDdense",
+                                                 "qfrc_constraint", "qacc", "solver_niter"] + ROW_FIELDS + list(CON_FLOAT)}
+        rec["ncon"], rec["nefc"] = o.ncon, o.nefc
+        out.append(rec)
+    return out
+
+
+@pytest.fixture(scope="module")
+def rows(models):
+    cache = {}
+
+    def get(name, nw=32, seed=1234, spread=0.9):
+        key = (name, nw, seed, spread)
+        if key not in cache:
+            m = models(name)
+            qpos, qvel, act, ctrl = parity.random_state(m, nw, seed, qpos_spread=spread)
+            ref = oracle_rows(m, qpos, qvel, act, ctrl)
+            model, d, got = parity.gpu_forward(m, qpos, qvel, act, ctrl, nconmax=32, njmax=160)
+            cache[key] = (m, ref, got)
+        return cache[key]
+    return get
+
+
+def _scale(ref, k):
+    v = [np.abs(r[k]).max() for r in ref if r[k].size]
+    return max(max(v) if v else 0.0, 1e-12)
+
+
+@pytest.mark.parametrize("name", MODELS)
+def test_constraint_rows_by_value(rows, name):
+    m, ref, got = rows(name)
+    nw, nv = len(ref), m.nv
+    njmax = got.efc_type.shape[1]
+    sJ = _scale(ref, "efc_J")
+    sc = {k: _scale(ref, k) for k in ROW_FIELDS}
+    gJ = got.efc_j.reshape(nw, njmax, nv)
+    for w in range(nw):
+        n = ref[w]["nefc"]
+        assert int(got.nefc[w, 0]) == n
+        assert np.array_equal(got.efc_type[w, :n], ref[w]["efc_type"]), f"world {w}: efc_type"
+        assert np.all(got.efc_type[w, n:] == -1), "efc_type padding"
+        assert np.abs(gJ[w, :n] - ref[w]["efc_J"].reshape(n, nv)).max(initial=0) <= 1e-4 * sJ, f"world {w}: efc_J"
+        assert not gJ[w, n:].any(), "efc_J padding"
+        for k in ("efc_pos", "efc_margin", "efc_aref"):
+            g = getattr(got, k.lower())[w]
+            assert np.abs(g[:n] - ref[w][k]).max(initial=0) <= 1e-4 * sc[k] + 1e-7, f"world {w}: {k}"
+            assert not g[n:].any(), f"{k} padding"
+        gD = got.efc_d[w]
+        assert np.all(np.abs(gD[:n] - ref[w]["efc_D"]) <= 2e-4 * np.abs(ref[w]["efc_D"])), f"world {w}: efc_D"
+        assert not gD[n:].any() and not got.efc_force[w, n:].any()
+
+
+@pytest.mark.parametrize("name", MODELS)
+def test_contact_records_by_value(rows, name):
+    m, ref, got = rows(name)
+    nw = len(ref)
+    for w in range(nw):
+        n = ref[w]["ncon"]
+        assert int(got.ncon[w, 0]) == n
+        assert np.array_equal(got.contact_dim[w, :n], ref[w]["contact_dim"]), f"world {w}: contact_dim"
+        assert np.array_equal(got.contact_efc_address[w, :n], ref[w]["contact_efc_address"]), f"world {w}: contact_efc_address"
+        assert np.all(got.contact_dim[w, n:] == 0) and np.all(got.contact_efc_address[w, n:] == -1)
+        for k, width in CON_FLOAT.items():
+            g = getattr(got, k).reshape(nw, -1, width)[w]
+            np.testing.assert_allclose(g[:n], ref[w][k].reshape(n, width), rtol=1e-6, atol=1e-7, err_msg=f"world {w}: {k}")
+            assert not g[n:].any(), f"{k} padding"
+
+
+@pytest.mark.parametrize("name", MODELS)
+def test_factor_and_constraint_forces(rows, models, name):
+    m, ref, got = rows(name)
+    nw, nv = len(ref), m.nv
+    sL = _scale(ref, "qLDdense")
+    for w in range(nw):
+        assert np.abs(got.qld[w].reshape(nv, nv) - ref[w]["qLDdense"].reshape(nv, nv)).max() <= 1e-4 * sL, f"world {w}: qLD"
+    # forces of the Newton solve: judged like qacc (tests/test_parity_gpu.py::test_constrained_acceleration), float32 oracle as yardstick
+    qpos, qvel, act, ctrl = parity.random_state(m, nw, 1234, qpos_spread=0.9)
+    reff, _ = parity.oracle_forward(m, qpos, qvel, act, ctrl, ["qfrc_constraint"], use_float=True)
+    sF, sQ = _scale(ref, "efc_force"), _scale(ref, "qfrc_constraint")
+    bad = 0
+    for w in range(nw):
+        n = ref[w]["nefc"]
+        eF = np.abs(got.efc_force[w, :n] - ref[w]["efc_force"]).max(initial=0) / sF
+        eQ = np.abs(got.qfrc_constraint[w] - ref[w]["qfrc_constraint"]).max() / sQ
+        e32 = np.abs(reff["qfrc_constraint"][w] - ref[w]["qfrc_constraint"]).max() / sQ
+        if n == 0:
+            assert eQ == 0
+        if (eF > 2e-3 or eQ > 2e-3) and e32 < 5e-4:
+            bad += 1
+    assert bad <= max(1, nw // 16), f"{name}: {bad} worlds with constraint forces beyond 2e-3"
+
+
+@pytest.mark.parametrize("name", ["hand", "legs"])
+def test_solver_iterations_close_to_oracle(rows, models, name):
+    """solver_niter: float32 stops on its noise floors (GRAD_NOISE / LS_NOISE), the float64 oracle on MuJoCo's
+    tolerance, so counts may differ by an iteration; the float32 build of the oracle is the like-for-like yardstick."""
+    m, ref, got = rows(name)
+    nw = len(ref)
+    qpos, qvel, act, ctrl = parity.random_state(m, nw, 1234, qpos_spread=0.9)
+    import oracle
+    o = oracle.Oracle(m, use_float=True)
+    n32 = []
+    for w in range(nw):
+        o.set_state(qpos[w], qvel[w], act[w], ctrl[w], np.zeros(m.nv)); o.forward(); n32.append(int(o.solver_niter[0]))
+    g = got.solver_niter[:, 0]
+    n64 = np.array([int(r["solver_niter"][0]) for r in ref])
+    assert np.all((g > 0) == (n64 > 0)), "a world solved without rows, or skipped the solve with rows"
+    assert np.abs(g - np.array(n32)).max() <= 2 and np.mean(g == np.array(n32)) >= 0.5, f"gpu {g} f32 oracle {n32} f64 oracle {n64}"
+
+
+def test_benchmarked_shape_matches_oracle(models):
+    """BASELINE.json's headline shape: MyoHand (hand_pose), 8192 worlds, default kernel selection, full mjData.  64 sampled
+    worlds against the oracle: stage fields + integers after mj_forward, state after 1 and 10 steps."""
+    import oracle
+    import torch
+    from myosuite_mjx_b200 import mjx
+    m = models("hand_pose")
+    nw = 8192
+    qpos, qvel, act, ctrl = parity.random_state(m, nw, 4321, qpos_spread=0.9)
+    sample = np.linspace(0, nw - 1, 64).astype(int)
+    model = mjx.put_model(m)
+    d = mjx.put_data(model, dict(qpos=qpos, qvel=qvel, act=act, ctrl=ctrl), nworld=nw, fields="all")
+    mjx.forward(model, d)
+    torch.cuda.synchronize()
+    stage = ["xpos", "site_xpos", "ten_length", "ten_J", "actuator_force", "qM", "qfrc_bias", "qacc_smooth", "cdof", "cvel"]
+    ref, ex = parity.oracle_forward(m, qpos[sample], qvel[sample], act[sample], ctrl[sample], stage + ["qacc"])
+    idx = torch.as_tensor(sample, device="cuda")
+    for k in stage:
+        g = getattr(d, k.lower())[idx].double().cpu().numpy().reshape(ref[k].shape)
+        assert np.abs(g - ref[k]).max() <= 1e-4 * max(np.abs(ref[k]).max(), 1e-12), k
+    assert np.array_equal(d.ncon[idx, 0].cpu().numpy(), np.array(ex["ncon"])) and np.array_equal(d.nefc[idx, 0].cpu().numpy(), np.array(ex["nefc"]))
+    cg = d.contact_geom[idx].cpu().numpy().reshape(len(sample), -1, 2)
+    for i in range(len(sample)):
+        assert np.array_equal(cg[i, :ex["ncon"][i]], ex["contact_geom"][i])
+    sq = max(np.abs(ref["qacc"]).max(), 1e-9)
+    eq = np.abs(d.qacc[idx].double().cpu().numpy() - ref["qacc"]).max(axis=1) / sq
+    assert np.median(eq) < 5e-4 and (eq > 2e-3).sum() <= 4, eq
+    assert int((d.status != 0).sum()) == 0
+    # one step and ten steps from the same synchronised state
+    o = oracle.Oracle(m)
+    e = mjx.put_data(model, dict(qpos=qpos, qvel=qvel, act=act, ctrl=ctrl), nworld=nw, fields="all")
+    mjx.step(model, e, 1)
+    torch.cuda.synchronize()
+    q1, v1 = e.qpos[idx].double().cpu().numpy(), e.qvel[idx].double().cpu().numpy()
+    mjx.step(model, e, 9)
+    torch.cuda.synchronize()
+    q10 = e.qpos[idx].double().cpu().numpy()
+    for i, w in enumerate(sample[:24]):
+        o.reset(); o.set_state(qpos[w], qvel[w], act[w], ctrl[w]); o.step(1)
+        assert np.abs(q1[i] - o.qpos).max() < 1e-5 + 1e-3 * m.opt_timestep * np.abs(o.qvel).max()
+        assert np.abs(v1[i] - o.qvel).max() < 1e-3 * max(1.0, np.abs(o.qvel).max())
+        o.step(9)
+        assert np.abs(q10[i] - o.qpos).max() < 2e-3, f"world {w}: 10-step drift {np.abs(q10[i] - o.qpos).max()}"

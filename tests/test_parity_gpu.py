@@ -243,63 +243,41 @@ def test_fused_substeps_equal_repeated_steps(models):
         assert torch.equal(getattr(a, f), getattr(b, f)), f"{f}: fused substeps differ from repeated launches"
 
 
-def test_two_ctas_per_sm_variant_equals_one(models, monkeypatch):
-    """Batches above 8288 worlds run the 8-lane kernel built for two co-resident CTAs per SM (<= 72 registers); it is the
-    same source, so a batch stepped by it must equal the one-CTA build bit for bit.  A large batch picks it by itself."""
+def test_phase_pipeline_equals_one_launch_kernel(models, monkeypatch):
+    """The default engine (lane = world phase kernels + 8-lane solver) and the one-launch kernel of round 1 (MYO_ENGINE=mono)
+    run the same per-item arithmetic in the same order: stepped batches agree bit for bit, for every team width of the solver."""
+    import gc
     import torch
     from myosuite_mjx_b200 import mjx
     m = models("hand")
     nw = 96
     qpos, qvel, act, ctrl = parity.random_state(m, nw, 5, qpos_spread=0.9)
     model = mjx.put_model(m)
-    import gc
-    names = ("qpos", "qvel", "act", "qacc_warmstart", "actuator_force", "ten_length", "ncon", "nefc", "contact_geom", "efc_force")
-    out = []
-    for ctas in (1, 2):   # one batch alive at a time: a batch holds one of the 8 constant-memory parameter slots
-        monkeypatch.setenv("MYO_TEAM", "8"); monkeypatch.setenv("MYO_CTAS", str(ctas))
+    names = ("qpos", "qvel", "act", "qacc_warmstart", "actuator_force", "ten_length", "ncon", "nefc", "contact_geom", "efc_force", "site_xpos", "efc_j", "qld", "wrap_xpos")
+    out = {}
+    for engine, team in (("mono", "8"), ("phase", "8"), ("phase", "4"), ("phase", "16")):
+        monkeypatch.setenv("MYO_ENGINE", engine); monkeypatch.setenv("MYO_TEAM", team)
         d = mjx.put_data(model, dict(qpos=qpos, qvel=qvel, act=act, ctrl=ctrl), nworld=nw, fields="all")
-        assert (d.team, d.ctas_per_sm) == (8, ctas)
+        assert (d.engine, d.team) == (engine, int(team))
         mjx.step(model, d, 3)
         torch.cuda.synchronize()
-        out.append({f: getattr(d, f).clone() for f in names})
+        out[(engine, team)] = {f: getattr(d, f).clone() for f in names}
         del d; gc.collect()
+    ref = out[("mono", "8")]
     for f in names:
-        assert torch.equal(out[0][f], out[1][f]), f"{f}: two-CTA build differs"
-    monkeypatch.delenv("MYO_TEAM"); monkeypatch.delenv("MYO_CTAS")
-    for nworld, want in ((8320, (8, 2)), (8192, (8, 1))):
-        b = mjx.make_data(model, nworld, "core")
-        got = (b.team, b.ctas_per_sm)
-        del b; gc.collect()
-        assert got == want
+        assert torch.equal(ref[f], out[("phase", "8")][f]), f"{f}: phase pipeline differs from the one-launch kernel"
+    for team in ("4", "16"):   # team width changes the summation order inside the solver only: state within float32 solver noise
+        for f in ("ncon", "nefc", "contact_geom"):
+            assert torch.equal(ref[f], out[("phase", team)][f]), f"{f}: team {team}"
+        assert (ref["qpos"] - out[("phase", team)]["qpos"]).abs().max() < 1e-4
+    monkeypatch.delenv("MYO_ENGINE"); monkeypatch.delenv("MYO_TEAM")
+    b = mjx.make_data(model, 8192, "core")
+    assert (b.engine, b.team) == ("phase", 8)
 
 
-def test_large_batch_fused_substeps_switch_builds(models):
-    """Above 8288 worlds a launch of one or two substeps runs the two-CTAs-per-SM build, a launch of three or more the
-    one-CTA build (co-resident CTAs drift apart over fused substeps); both are the same source, so the states agree bit for bit."""
-    import gc
-    import torch
-    from myosuite_mjx_b200 import mjx
-    m = models("hand")
-    nw = 8320
-    qpos, qvel, act, ctrl = parity.random_state(m, nw, 9, qpos_spread=0.6)
-    model = mjx.put_model(m)
-    a = mjx.put_data(model, dict(qpos=qpos, qvel=qvel, act=act, ctrl=ctrl), nworld=nw, fields="core")
-    assert (a.team, a.ctas_per_sm) == (8, 2)
-    mjx.step(model, a, 4)
-    torch.cuda.synchronize()
-    ref = {f: getattr(a, f).clone() for f in ("qpos", "qvel", "act", "qacc_warmstart")}
-    del a; gc.collect()
-    b = mjx.put_data(model, dict(qpos=qpos, qvel=qvel, act=act, ctrl=ctrl), nworld=nw, fields="core")
-    for _ in range(4):
-        mjx.step(model, b, 1)
-    torch.cuda.synchronize()
-    for f, v in ref.items():
-        assert torch.equal(getattr(b, f), v), f"{f}: fused launch (one CTA per SM) differs from single-step launches (two CTAs per SM)"
-    del b; gc.collect()
-
-
-def test_pipelined_outputs_equal_stream_ordered(models):
-    """myo_batch_set_pipelined: the wide-output kernel of step k runs on a side stream under step k+1 (two scratch buffers);
+def test_pipelined_outputs_equal_stream_ordered(models, monkeypatch):
+    """(one-launch engine, MYO_ENGINE=mono; the phase pipeline writes every field from the phase that produces it and has
+    no separate output kernel to pipeline: there the switch is accepted and changes nothing)  myo_batch_set_pipelined: the wide-output kernel of step k runs on a side stream under step k+1 (two scratch buffers);
     after the join every field equals the stream-ordered default bit for bit, also across masked / posvel passes and resets."""
     import gc
     import torch
@@ -309,6 +287,7 @@ def test_pipelined_outputs_equal_stream_ordered(models):
     qpos, qvel, act, ctrl = parity.random_state(m, nw, 13, qpos_spread=0.9)
     model = mjx.put_model(m)
     mask = torch.zeros(nw, dtype=torch.int32, device="cuda"); mask[::3] = 1
+    monkeypatch.setenv("MYO_ENGINE", "mono")
     snaps = []
     for pipelined in (False, True):
         d = mjx.put_data(model, dict(qpos=qpos, qvel=qvel, act=act, ctrl=ctrl), nworld=nw, fields="all")
