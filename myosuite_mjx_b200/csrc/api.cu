@@ -273,8 +273,9 @@ static int launchPhases(myo_batch* b, int nsub, int forward_only, const int32_t*
     }
     ok &= tile(MYO_K_VELACT, fslot, posvel ? 1 : 0) == 0;
     if (posvel) break;
-    g_launches++;
-    ok &= b->kern->solve(slot, fslot, b->L, nw, st, mask, forward_only ? 0 : 1, scr, stream) == 0;
+    static const bool team_solver = getenv("MYO_SOLVER") && std::string(getenv("MYO_SOLVER")) == "team";   // developer knob: the TEAM-mode solver
+    if (team_solver) { g_launches++; ok &= b->kern->solve(slot, fslot, b->L, nw, st, mask, forward_only ? 0 : 1, scr, stream) == 0; }
+    else ok &= tile(MYO_K_NEWTON, fslot, (forward_only ? 0 : 1) | (b->D.nv << 8)) == 0;
     if (last && b->wide) ok &= tile(MYO_K_CONOUT, fslot, 0) == 0;
     ok &= tile(MYO_K_FINISH, fslot, (forward_only ? 0 : MYO_FIN_EULER) | (last && (!forward_only || do_reset) ? MYO_FIN_STATE : 0) |
                                         (last ? MYO_FIN_WARM | MYO_FIN_ACC : 0)) == 0;

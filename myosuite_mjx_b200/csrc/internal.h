@@ -32,7 +32,7 @@ MYO_DECLARE_TEAM(4)
 MYO_DECLARE_TEAM(8)
 MYO_DECLARE_TEAM(16)
 // TILE-mode kernels (tile.cu, lane = world): one entry per phase of the pipeline
-enum { MYO_K_KIN = 0, MYO_K_TENDON, MYO_K_INERTIA, MYO_K_COLLIDE, MYO_K_VELACT, MYO_K_FINISH, MYO_K_CONOUT };
+enum { MYO_K_KIN = 0, MYO_K_TENDON, MYO_K_INERTIA, MYO_K_COLLIDE, MYO_K_VELACT, MYO_K_FINISH, MYO_K_CONOUT, MYO_K_NEWTON };
 enum { MYO_KIN_LOAD = 1, MYO_KIN_RESET = 2, MYO_KIN_CHECK = 4 };                 // flags of MYO_K_KIN
 enum { MYO_FIN_EULER = 1, MYO_FIN_STATE = 2, MYO_FIN_WARM = 4, MYO_FIN_ACC = 8 };  // flags of MYO_K_FINISH
 int myo_tile_upload(int slot, const DevModel& D, const SmemLayout& L, const FieldPtrs& F, void* stream);

@@ -18,17 +18,11 @@ namespace {
 // [TRI(nv)][HS] tile per warp -- whenever the CTA's tiles fit (hshared, set at upload), else in the scratch.
 // Only the lower triangle is stored, row-packed: element (r, c <= r) at TRI(r) + c.
 #define HS (32 / TEAM)
-#define TRI(r) (((r) * ((r) + 1)) >> 1)
 extern __shared__ float ctaShared[];
 __device__ __forceinline__ SP hessian(SP sm, int offH, int nv, int hshared) {
   if (!hshared) return sm + offH;
   SP r; r.p = ctaShared + (threadIdx.x >> 5) * (TRI(nv) * HS) + (threadIdx.x & 31) / TEAM; r.s = HS;
   return r;
-}
-__device__ __forceinline__ float teamSum(Tm t, float v) {
-#pragma unroll
-  for (int o = TEAM / 2; o > 0; o >>= 1) v += __shfl_xor_sync(t.mask, v, o);
-  return v;
 }
 __device__ __forceinline__ int teamMinI(Tm t, int v) {
 #pragma unroll
@@ -150,61 +144,6 @@ __device__ __noinline__ int collision(int slot, SP sm, Tm t, int* status) {
   TSYNC();
   return ncon;
 }
-// ------------------------------------------------------------------------------------------ constraints
-// Rows are never stored densely: a row is (type, id, coef) and its Jacobian is implied -- limit rows are 1-sparse,
-// equality rows 2-sparse, tendon-limit rows reuse the tendon's sparse moment-arm row, contact rows are +- combinations
-// of the contact's base rows (normal, 2 tangents, torsion) held in conJ.
-
-__device__ __noinline__ float impedance(const float* si, float x) {  // si = sanitised solimp, x = |pos - margin|
-  const float dmin = si[0], dmax = si[1], width = si[2], mid = si[3], power = si[4];
-  if (dmin == dmax || width <= MINVAL) return 0.5f * (dmin + dmax);
-  x = x / width;
-  if (x >= 1.f) return dmax;
-  if (x <= 0.f) return dmin;
-  float y;
-  if (power == 1.f) y = x;
-  else if (x <= mid) y = pow_(x, power) / pow_(mid, power - 1.f);
-  else y = 1.f - pow_(1.f - x, power) / pow_(1.f - mid, power - 1.f);
-  return dmin + y * (dmax - dmin);
-}
-__device__ __noinline__ void setRow(int slot, SP sm, int r, int type, int id, float coef, int desc1,
-                                    float pos, float margin, float dA, const float* kb, float vel, float Rscale) {
-  const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
-  const float imp = impedance(kb + 2, fabsf(pos - margin));   // kb: K, B, solimp[5]
-  float R = fmaxf(MINVAL, (1.f - imp) * dA / imp);
-  if (Rscale > 0.f) R = fmaxf(MINVAL, Rscale * R);
-  EFC(E_D, r) = 1.f / R;
-  EFC(E_AREF, r) = -kb[1] * vel - kb[0] * imp * (pos - margin);
-  EFC(E_DESC0, r) = __int_as_float(type | (id << 2)); EFC(E_COEF, r) = coef; EFC(E_DESC1, r) = __int_as_float(desc1);
-  EFC(E_POS, r) = pos; EFC(E_MARGIN, r) = margin; EFC(E_FORCE, r) = 0.f;
-}
-// base-row products  out[b] = conJ[b] . x   for the nb*ncon contact base rows
-__device__ __noinline__ void baseMul(int slot, SP sm, Tm t, int ncon, SP x, SP out) {
-  const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
-  const int nbr = D.maxbase * ncon, nv = D.nv;
-  TFOR(b, nbr) {
-    auto J = sm + L.conJ + b * nv;
-    float a0 = 0.f, a1 = 0.f;
-    int k = 0;
-    for (; k + 1 < nv; k += 2) { a0 = fmaf(J[k], x[k], a0); a1 = fmaf(J[k + 1], x[k + 1], a1); }
-    if (k < nv) a0 = fmaf(J[k], x[k], a0);
-    out[b] = a0 + a1;
-  }
-}
-// J_r . x for one efc row (bx = base products of x)
-__device__ __forceinline__ float rowMul(int slot, SP sm, int r, SP x, SP bx) {
-  const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
-  const int d0 = EFCI(E_DESC0, r), type = d0 & 3, id = d0 >> 2;
-  const float coef = EFC(E_COEF, r);
-  if (type == ROW_LIMJ) return coef * x[D.limj_dof[id]];
-  if (type == ROW_CON) { const int q = EFCI(E_DESC1, r); return bx[id] + (q >= 0 ? coef * bx[q] : 0.f); }
-  if (type == ROW_EQ) { const int d2 = D.eq_dof2[id]; return x[D.eq_dof1[id]] + (d2 >= 0 ? coef * x[d2] : 0.f); }
-  const int tn = D.limt_ten[id];
-  float acc = 0.f;
-  for (int n = D.ten_nzstart[tn]; n < D.ten_nzstart[tn + 1]; n++) acc += sm[L.tenJ + n] * x[D.nz_dof[n]];
-  return coef * acc;
-}
-
 __device__ __noinline__ int makeConstraint(int slot, SP sm, Tm t, int ncon, int* status) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
   const int nv = D.nv, njmax = D.njmax;
@@ -325,79 +264,6 @@ __device__ __noinline__ int makeConstraint(int slot, SP sm, Tm t, int ncon, int*
   return nefc;
 }
 
-// ------------------------------------------------------------------------------------------ Newton solver (mj_fwdConstraint)
-__device__ __noinline__ void mulMsparse(int slot, SP qM, SP x, SP out, Tm t) {
-  const DevModel& D = tP[slot].D;
-  TFOR(i, D.nv) {
-    const int a = D.dof_Madr[i], d = D.dof_rowlen[i];
-    float acc = 0.f;
-    for (int q = 0; q < d; q++) acc = fmaf(qM[a + q], x[D.M_col[a + q]], acc);
-    for (int e = D.desc_start[i]; e < D.desc_start[i + 1]; e++) acc = fmaf(qM[D.desc_idx[e]], x[D.desc_dof[e]], acc);
-    out[i] = acc;
-  }
-}
-__device__ __forceinline__ bool rowOn(int d0, float jar) { return ((d0 & 3) == ROW_EQ) || jar < 0.f; }
-// jar = J x - aref for all rows, returns the (team-uniform) constraint cost; force/active are implied by jar
-__device__ __noinline__ float residualCost(int slot, SP sm, Tm t, int ncon, int nefc, SP x) {
-  const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
-  auto bx = sm + L.basev;
-  baseMul(slot, sm, t, ncon, x, bx);
-  TSYNC();
-  float cost = 0.f;
-  TFOR(r, nefc) {
-    const float jar = rowMul(slot, sm, r, x, bx) - EFC(E_AREF, r);
-    EFC(E_JAR, r) = jar;
-    if (rowOn(EFCI(E_DESC0, r), jar)) cost = fmaf(0.5f * EFC(E_D, r) * jar, jar, cost);
-  }
-  TSYNC();
-  return teamSum(t, cost);
-}
-// forces from jar, then out = J^T f  (deterministic gathers, no atomics)
-__device__ __noinline__ void constraintForce(int slot, SP sm, Tm t, int ncon, int nefc, SP out) {
-  const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
-  const int nv = D.nv, nb = D.maxbase;
-  TFOR(r, nefc) { const float jar = EFC(E_JAR, r); EFC(E_FORCE, r) = rowOn(EFCI(E_DESC0, r), jar) ? -EFC(E_D, r) * jar : 0.f; }
-  TSYNC();
-  auto bf = sm + L.basev + nb * D.nconmax;
-  TFOR(b, nb * ncon) {
-    const int c = b / nb, k = b - c * nb;
-    auto cr = sm + L.con + 12 * c;
-    const int adr = __float_as_int(cr[8]), dim = __float_as_int(cr[9]);
-    float f = 0.f;
-    if (adr >= 0 && k < dim) {
-      if (dim == 1) f = EFC(E_FORCE, adr);
-      else if (k == 0) { for (int p = 0; p < 2 * (dim - 1); p++) f += EFC(E_FORCE, adr + p); }
-      else f = EFC(E_COEF, adr + 2 * (k - 1)) * (EFC(E_FORCE, adr + 2 * (k - 1)) - EFC(E_FORCE, adr + 2 * (k - 1) + 1));
-    }
-    bf[b] = f;
-  }
-  TSYNC();
-  TFOR(k, nv) {
-    float acc = 0.f;
-    for (int e = D.dofeq_start[k]; e < D.dofeq_start[k + 1]; e++) {
-      const int v = D.dofeq_list[e], r = v >> 1;
-      acc += (v & 1) ? EFC(E_COEF, r) * EFC(E_FORCE, r) : EFC(E_FORCE, r);
-    }
-    const int li = D.dof_limidx[k];
-    if (li >= 0)
-      for (int q = 0; q < 2; q++) { const int r = __float_as_int(sm[L.limrow + 2 * li + q]); if (r >= 0) acc += EFC(E_COEF, r) * EFC(E_FORCE, r); }
-    if (D.nlimt > 0)
-      for (int c = D.col_start[k]; c < D.col_start[k + 1]; c++) {
-        const int n = D.col_nz[c], lt = D.ten_limidx[D.nz_tendon[n]];
-        if (lt < 0) continue;
-        for (int q = 0; q < 2; q++) {
-          const int r = __float_as_int(sm[L.limrow + 2 * (D.nlimj + lt) + q]);
-          if (r >= 0) acc += EFC(E_COEF, r) * EFC(E_FORCE, r) * sm[L.tenJ + n];
-        }
-      }
-    float a1 = 0.f;
-    int b = 0;
-    for (; b + 1 < nb * ncon; b += 2) { acc = fmaf(sm[L.conJ + b * nv + k], bf[b], acc); a1 = fmaf(sm[L.conJ + (b + 1) * nv + k], bf[b + 1], a1); }
-    if (b < nb * ncon) acc = fmaf(sm[L.conJ + b * nv + k], bf[b], acc);
-    out[k] = acc + a1;
-  }
-  TSYNC();
-}
 // H = M + J^T D_active J (lower triangle), Cholesky in place
 __device__ __noinline__ void hessianFactor(int slot, SP sm, Tm t, int ncon, int nefc) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
@@ -507,31 +373,6 @@ __device__ __noinline__ void hessianFactor(int slot, SP sm, Tm t, int ncon, int 
     TSYNC();
   }
 }
-__device__ __noinline__ void cholSolve(int slot, SP H, SP x, Tm t) {
-  const int nv = tP[slot].D.nv;
-  for (int j = 0; j < nv; j++) {
-    const float xj = x[j] / H[TRI(j) + j];
-    TSYNC();
-    if (t.tl == 0) x[j] = xj;
-    for (int r = j + 1 + t.tl; r < nv; r += TEAM) x[r] = fmaf(-H[TRI(r) + j], xj, x[r]);
-    TSYNC();
-  }
-  for (int j = nv - 1; j >= 0; j--) {
-    const float xj = x[j] / H[TRI(j) + j];
-    TSYNC();
-    if (t.tl == 0) x[j] = xj;
-    for (int r = t.tl; r < j; r += TEAM) x[r] = fmaf(-H[TRI(j) + r], xj, x[r]);
-    TSYNC();
-  }
-}
-// One point of the 1-D cost along the search direction.  `tol` is the convergence threshold for |d0| at this point:
-// MuJoCo's gtol, or the float32 noise floor of the derivative sum when that is larger (the sum cancels to ~eps * mag
-// at the minimiser; without the floor the search burns all ls_iterations chasing rounding noise -- measured on the
-// float build of the oracle: 34 evaluations per search instead of the double build's 2.8).
-#ifndef LS_NOISE
-#define LS_NOISE 2e-6f
-#endif
-struct LsPt { float alpha, cost, d0, d1, tol; };
 __device__ __noinline__ LsPt lsEval(int slot, SP sm, Tm t, int nefc, float a, const float* qg, float gtol) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
   float q0 = 0.f, q1 = 0.f, q2 = 0.f, qa = 0.f;
@@ -676,57 +517,6 @@ __device__ __forceinline__ bool anyBad(SP v, int n, Tm t) {
   bool bad = false;
   TFOR(i, n) bad |= !(fabsf(v[i]) < 1e10f);
   return teamAny(t, bad);
-}
-// ------------------------------------------------------------------------------------------ touch sensors (mj_sensorAcc)
-// sensordata[s] = sum of the normal forces of the active contacts that involve the sensor site's body and whose
-// normal ray (from the contact point, pointing into that body's side) meets the site's zone.  The pyramidal normal
-// force is the sum of the contact's row forces (mju_decodePyramid).
-__device__ __noinline__ void touchSensors(int slot, int fslot, SP sm, Tm t, World W, int ncon) {
-  const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L; const FieldPtrs& F = tP[fslot].F;
-  void* out = F.p[MYO_F_SENSORDATA];
-  if (!out) return;
-  TFOR(s, D.nsensor) {
-    const int sid = D.sens_site[s], body = D.sens_body[s], f = D.site_frame[sid];
-    const f3 spos = ld3(FR_POS(sm, L, f)) + mulM(FR_MAT(sm, L, f), ld3(D.site_lpos + 3 * sid));
-    float R[9]; mulMM(R, FR_MAT(sm, L, f), D.site_lmat + 9 * sid);
-    const f3 size = ld3(D.sens_size + 3 * s);
-    float total = 0.f;
-    for (int c = 0; c < ncon; c++) {
-      auto cr = sm + L.con + 12 * c;
-      const int adr = __float_as_int(cr[8]), dim = __float_as_int(cr[9]), pr = __float_as_int(cr[7]);
-      if (adr < 0) continue;
-      const int b1 = D.cg_body[D.pair_cg1[pr]], b2 = D.cg_body[D.pair_cg2[pr]];
-      if (body != b1 && body != b2) continue;
-      float fn = 0.f;
-      const int rows = dim == 1 ? 1 : 2 * (dim - 1);
-      for (int q = 0; q < rows; q++) fn += EFC(E_FORCE, adr + q);
-      if (!(fn > 0.f)) continue;
-      f3 dir = unit3(ld3(cr + 4) * fn);
-      if (body == b2) dir = dir * -1.f;
-      const f3 p = mulMT(R, ld3(cr + 1) - spos), v = mulMT(R, dir);   // ray in the site's frame
-      bool hit;
-      if (D.sens_type[s] == G_SPHERE) {
-        const float b = dot(p, v), cc = dot(p, p) - size.x * size.x, disc = b * b - cc;
-        hit = disc >= 0.f && (-b + sqrtf(disc)) >= 0.f;
-      } else {   // box: slab test, the ray t >= 0 meets the solid box
-        float t0 = 0.f, t1 = 3.4e38f;
-        const float pp[3] = {p.x, p.y, p.z}, vv[3] = {v.x, v.y, v.z}, hh[3] = {size.x, size.y, size.z};
-        hit = true;
-        for (int k = 0; k < 3; k++) {
-          if (fabsf(vv[k]) < MINVAL) { if (fabsf(pp[k]) > hh[k]) hit = false; }
-          else {
-            const float inv = 1.f / vv[k];
-            float a = (-hh[k] - pp[k]) * inv, b = (hh[k] - pp[k]) * inv;
-            if (a > b) { const float tmp = a; a = b; b = tmp; }
-            t0 = fmaxf(t0, a); t1 = fminf(t1, b);
-          }
-        }
-        hit = hit && t0 <= t1;
-      }
-      if (hit) total += fn;
-    }
-    OUTF(out, s) = total;
-  }
 }
 // ------------------------------------------------------------------------------------------ solveKernel (phase pipeline)
 // The data-dependent middle of a step: constraint rows, Newton solve, mj_checkAcc, touch sensors.  Reads what the TILE

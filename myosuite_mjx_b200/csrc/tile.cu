@@ -136,7 +136,7 @@ __global__ void __launch_bounds__(512) velactKernel(int slot, int fslot, int nwo
 // item range, counts its survivors per lane, the per-warp counts meet in shared memory, and every warp then writes its
 // survivors starting at its lane's exclusive prefix.  The convex narrow phase (MPR, float64, long) is listed per lane
 // first and run afterwards, so the lanes of a warp that have an MPR pair run it at the same time.
-#define MAXW 16   // warps per tile CTA (blockDim <= 512)
+
 __device__ __forceinline__ bool broadPass(const DevModel& D, const SmemLayout& L, SP sm, int pr) {
   const int c1 = D.pair_cg1[pr], c2 = D.pair_cg2[pr];
   auto P1 = sm + L.cgpose + 12 * c1; auto P2 = sm + L.cgpose + 12 * c2;
@@ -249,6 +249,544 @@ __global__ void __launch_bounds__(512) collideKernel(int slot, int nworld, int s
       ncon = D.nconmax;
     }
     sm[L.counts] = __int_as_float(ncon);
+  }
+}
+
+// ------------------------------------------------------------------------------------------ newton: mj_makeConstraint, mj_fwdConstraint
+// The data-dependent middle of the step with LANE = WORLD as well.  Loops over a world's rows / contacts take the lane's
+// own count as bound (lanes with fewer rows idle, no barrier inside such a loop); every barrier and every shared-memory
+// sum sits in CTA-uniform control flow, whose bounds are the tile's maxima (warp reductions of per-lane values that are
+// identical in every warp of the tile).  A world that has converged is masked out and the tile iterates until its slowest
+// world is done.  Per-lane scalars (cost, step size, iteration count, flags) are replicated in every warp: they come from
+// sums that are bit-identical in all warps, so all warps take the same branches.
+struct TileScan { int off, total; };
+// exclusive prefix of a per-(warp, lane) count over the warps of the tile, in warp order: warp j owns a contiguous chunk
+// of an item range, so per-lane ordered compaction needs no serial walk
+__device__ __noinline__ TileScan tileScan(Tm t, int cnt) {
+  __shared__ int sc[MAXW][32];
+  const int lane = threadIdx.x & 31;
+  sc[t.tl][lane] = cnt;
+  __syncthreads();
+  TileScan r; r.off = 0; r.total = 0;
+  for (int j = 0; j < t.nw; j++) { const int v = sc[j][lane]; if (j < t.tl) r.off += v; r.total += v; }
+  __syncthreads();
+  return r;
+}
+__device__ __noinline__ int tileMinI(Tm t, int v) {
+  __shared__ int sc[MAXW][32];
+  const int lane = threadIdx.x & 31;
+  sc[t.tl][lane] = v;
+  __syncthreads();
+  int m = 0x7fffffff;
+  for (int j = 0; j < t.nw; j++) m = min(m, sc[j][lane]);
+  __syncthreads();
+  return m;
+}
+// N sums at once (one pair of barriers)
+#define MAXSUM 12
+__device__ __forceinline__ float* tileRedBuf() { __shared__ float red[MAXSUM * MAXW * 32]; return red; }   // one buffer for every N
+template <int N> __device__ __forceinline__ void tileSumN(Tm t, float* v) {
+  float* red = tileRedBuf() + (threadIdx.x & 31);
+#pragma unroll
+  for (int k = 0; k < N; k++) red[(k * MAXW + t.tl) * 32] = v[k];
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < N; k++) { float s = 0.f; for (int j = 0; j < t.nw; j++) s += red[(k * MAXW + j) * 32]; v[k] = s; }
+  __syncthreads();
+}
+
+__device__ __forceinline__ void limitState(const DevModel& D, const SmemLayout& L, SP sm, int li, float* dlo, float* dhi, float* margin, const float** prm) {
+  const bool isj = li < D.nlimj;
+  *prm = isj ? D.limj_prm + 12 * li : D.limt_prm + 12 * (li - D.nlimj);
+  const float val = isj ? sm[L.qpos + D.limj_q[li]] : sm[L.tenlen + D.limt_ten[li - D.nlimj]];
+  *margin = (*prm)[2]; *dlo = val - (*prm)[0]; *dhi = (*prm)[1] - val;
+}
+__device__ __forceinline__ int contactRows(const DevModel& D, const SmemLayout& L, SP sm, int c) {
+  auto cr = sm + L.con + 12 * c;
+  const int pr = __float_as_int(cr[7]), dim = __float_as_int(cr[9]);
+  const float inc = D.pair_prm[16 * pr] - D.pair_prm[16 * pr + 1];
+  return cr[0] < inc ? (dim == 1 ? 1 : 2 * (dim - 1)) : 0;
+}
+// mj_makeConstraint: rows in MuJoCo's order (equality, joint limits, tendon limits, contacts); returns the lane's nefc
+__device__ __noinline__ int makeConstraintTile(int slot, SP sm, Tm t, int ncon, int nconT, int* status) {
+  const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
+  const int nv = D.nv, njmax = D.njmax, nw = t.nw;
+  auto qpos = sm + L.qpos; auto qvel = sm + L.qvel;
+  if (D.disableflags & DSBL_CONSTRAINT) return 0;
+  TFOR(e, D.neq) {
+    const int d1 = D.eq_dof1[e], d2 = D.eq_dof2[e], q1 = D.eq_q1[e], q2 = D.eq_q2[e];
+    auto dt = D.eq_data + 5 * e;
+    float pos, dpoly = 0.f, vel = qvel[d1];
+    if (d2 >= 0) {
+      const float x = qpos[q2] - D.qpos0[q2];
+      pos = qpos[q1] - D.qpos0[q1] - (dt[0] + x * (dt[1] + x * (dt[2] + x * (dt[3] + x * dt[4]))));
+      dpoly = dt[1] + x * (2.f * dt[2] + x * (3.f * dt[3] + x * 4.f * dt[4]));
+      vel -= dpoly * qvel[d2];
+    } else pos = qpos[q1] - D.qpos0[q1] - dt[0];
+    setRow(slot, sm, e, ROW_EQ, e, -dpoly, 0, pos, 0.f, D.eq_prm[8 * e + 7], D.eq_prm + 8 * e, vel, 0.f);
+  }
+  int nefc = D.neq;
+  // ---- joint limits, then tendon limits
+  const int nlim = D.nlimj + D.nlimt;
+  if (nlim > 0) {
+    const int chunk = (nlim + nw - 1) / nw, l0 = min(nlim, t.tl * chunk), l1 = min(nlim, l0 + chunk);
+    int cnt = 0;
+    for (int li = l0; li < l1; li++) {
+      float dlo, dhi, margin; const float* prm;
+      limitState(D, L, sm, li, &dlo, &dhi, &margin, &prm);
+      cnt += (dlo < margin) + (dhi < margin);
+    }
+    const TileScan sc = tileScan(t, cnt);
+    int at = nefc + sc.off;
+    for (int li = l0; li < l1; li++) {
+      float dlo, dhi, margin; const float* prm;
+      limitState(D, L, sm, li, &dlo, &dhi, &margin, &prm);
+      int r0 = -1, r1 = -1;
+      if ((dlo < margin) || (dhi < margin)) {
+        const bool isj = li < D.nlimj;
+        const float v = isj ? qvel[D.limj_dof[li]] : sm[L.tenvel + D.limt_ten[li - D.nlimj]];
+        const int id = isj ? li : li - D.nlimj, type = isj ? ROW_LIMJ : ROW_LIMT;
+        if (dlo < margin) { if (at < njmax) { r0 = at; setRow(slot, sm, at, type, id, 1.f, 0, dlo, margin, prm[10], prm + 3, v, 0.f); } at++; }
+        if (dhi < margin) { if (at < njmax) { r1 = at; setRow(slot, sm, at, type, id, -1.f, 0, dhi, margin, prm[10], prm + 3, -v, 0.f); } at++; }
+      }
+      sm[L.limrow + 2 * li] = __int_as_float(r0); sm[L.limrow + 2 * li + 1] = __int_as_float(r1);
+    }
+    nefc += sc.total;
+  }
+  // ---- contacts: row addresses, base Jacobian rows, pyramid rows
+  if (nconT > 0) {
+    const int nb = D.maxbase;
+    const int chunk = (nconT + nw - 1) / nw, c0 = min(nconT, t.tl * chunk), c1 = min(nconT, c0 + chunk);
+    int cnt = 0;
+    for (int c = c0; c < c1; c++) cnt += c < ncon ? contactRows(D, L, sm, c) : 0;
+    const TileScan sc = tileScan(t, cnt);
+    int at = nefc + sc.off, unfit = 0x7fffffff;
+    for (int c = c0; c < c1; c++) {
+      if (c >= ncon) break;
+      const int rows = contactRows(D, L, sm, c);
+      sm[L.con + 12 * c + 8] = __int_as_float((rows > 0 && at + rows <= njmax) ? at : -1);
+      if (rows > 0 && at + rows > njmax) unfit = min(unfit, at);
+      at += rows;
+    }
+    nefc += sc.total;
+    // a contact that does not fit is dropped whole, and so is every later one (their addresses lie beyond njmax): the
+    // rows that exist are [0, unfit), all written below
+    unfit = tileMinI(t, unfit);
+    if (unfit < nefc) { *status |= MYO_WORLD_NEFC_OVERFLOW; nefc = min(unfit, njmax); }
+    // base Jacobian rows: one item = (contact, dof); contacts past the lane's own count up to the tile's get zero rows
+    // (the Hessian product below runs over the tile's count)
+    for (int idx = t.tl; idx < nconT * nv; idx += nw) {
+      const int c = idx / nv, k = idx - c * nv;
+      auto cr = sm + L.con + 12 * c;
+      auto J = sm + L.conJ + (c * nb) * nv + k;
+      if (c >= ncon || !(((unsigned)__float_as_int(cr[10 + (k >> 5)]) >> (k & 31)) & 1u)) {   // dof k moves both bodies or neither
+        J[0] = 0.f; if (nb > 1) { J[nv] = 0.f; J[2 * nv] = 0.f; } if (nb > 3) J[3 * nv] = 0.f; continue;
+      }
+      const int f1 = D.cg_frame[D.pair_cg1[__float_as_int(cr[7])]];
+      const int in1 = (D.fr_mask[2 * f1 + (k >> 5)] >> (k & 31)) & 1;   // it moves exactly one of them: the first (-) or the second (+)
+      const f3 pos = ld3(cr + 1), n = ld3(cr + 4);
+      f3 y, z; makeFrame(n, &y, &z);
+      const float sgn = in1 ? -1.f : 1.f;
+      auto cd = sm + L.cdof + 6 * k;
+      const f3 jr = ld3(cd) * sgn;
+      const f3 jp = (ld3(cd + 3) + cross(ld3(cd), pos - ld3(sm + L.rootcom + 3 * D.fr_root[D.dof_frame[k]]))) * sgn;
+      J[0] = dot(n, jp);
+      if (nb > 1) { J[nv] = dot(y, jp); J[2 * nv] = dot(z, jp); }
+      if (nb > 3) J[3 * nv] = dot(n, jr);
+    }
+    TSYNC();
+    auto bx = sm + L.basev;
+    baseMul(slot, sm, t, ncon, qvel, bx);
+    TSYNC();
+    for (int c = t.tl; c < ncon; c += nw) {
+      auto cr = sm + L.con + 12 * c;
+      const int adr = __float_as_int(cr[8]);
+      if (adr < 0) continue;
+      const int pr = __float_as_int(cr[7]), dim = __float_as_int(cr[9]);
+      auto pp = D.pair_prm + 16 * pr;
+      const float margin = pp[0] - pp[1], dist = cr[0];
+      const int g1 = D.pair_cg1[pr], g2 = D.pair_cg2[pr];
+      const float tran = D.cg_invweight[2 * g1] + D.cg_invweight[2 * g2];
+      const float kb[7] = {pp[14], pp[15], pp[9], pp[10], pp[11], pp[12], pp[13]};
+      const int bn = c * nb;
+      if (dim == 1) setRow(slot, sm, adr, ROW_CON, bn, 0.f, -1, dist, margin, tran, kb, bx[bn], 0.f);
+      else {
+        const float mu0 = pp[2] * rsqrtf(D.impratio);
+        const float dA0 = tran + pp[2] * pp[2] * tran;   // first pyramid row sets the shared regulariser
+        for (int k = 1; k < dim; k++) {
+          const float mu = pp[1 + k];
+          const int bt = bn + k;
+          setRow(slot, sm, adr + 2 * (k - 1), ROW_CON, bn, mu, bt, dist, margin, dA0, kb, bx[bn] + mu * bx[bt], 2.f * mu0 * mu0);
+          setRow(slot, sm, adr + 2 * (k - 1) + 1, ROW_CON, bn, -mu, bt, dist, margin, dA0, kb, bx[bn] - mu * bx[bt], 2.f * mu0 * mu0);
+        }
+      }
+    }
+  }
+  if (nefc > njmax) { *status |= MYO_WORLD_NEFC_OVERFLOW; nefc = njmax; }
+  TSYNC();
+  return nefc;
+}
+
+// H = M + J^T D_active J (lower triangle, row-packed) and its Cholesky factor; Hd receives the factor's diagonal.
+// Contacts enter through their base rows (normal, tangents, torsion): with W the small symmetric weight matrix of a
+// contact's active pyramid rows in base-row space, J^T D J = Jb^T (W Jb) =: Jb^T U, a dense [nv x nbase] x [nbase x nv]
+// product over the tile's nbase = maxbase * nconT base rows, done in 4 x 4 register blocks of H (one block per warp at a
+// time, the warps stream the same rows of U and Jb through L1 together).
+__device__ __noinline__ void hessianTile(int slot, SP sm, Tm t, SP H, SP Hd, int ncon, int nconT, int nefc) {
+  const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
+  const int nv = D.nv, nb = D.maxbase, nw = t.nw;
+  TFOR(i, TRI(nv)) H[i] = 0.f;
+  TSYNC();
+  TFOR(e, D.nM) H[TRI(D.M_row[e]) + D.M_col[e]] = sm[L.qM + e];
+  TSYNC();
+  TFOR(k, nv) {
+    const int li = D.dof_limidx[k];
+    if (li < 0) continue;
+    for (int q = 0; q < 2; q++) {
+      const int r = __float_as_int(sm[L.limrow + 2 * li + q]);
+      if (r >= 0 && EFC(E_JAR, r) < 0.f) H[TRI(k) + k] += EFC(E_D, r);
+    }
+  }
+  TSYNC();
+  if (t.tl == 0)
+    for (int e = 0; e < D.neq; e++) {
+      const int d1 = D.eq_dof1[e], d2 = D.eq_dof2[e];
+      const float Dr = EFC(E_D, e), c = EFC(E_COEF, e);
+      H[TRI(d1) + d1] += Dr;
+      if (d2 >= 0) { H[TRI(max(d1, d2)) + min(d1, d2)] += Dr * c; H[TRI(d2) + d2] += Dr * c * c; }
+    }
+  for (int lt = 0; lt < D.nlimt; lt++)
+    for (int q = 0; q < 2; q++) {
+      TSYNC();
+      const int r = __float_as_int(sm[L.limrow + 2 * (D.nlimj + lt) + q]);
+      if (r < 0 || !(EFC(E_JAR, r) < 0.f)) continue;   // per-lane; no barrier below in this iteration
+      const int tn = D.limt_ten[lt], n0 = D.ten_nzstart[tn], cnt = D.ten_nzstart[tn + 1] - n0;
+      const float Dr = EFC(E_D, r);
+      TFOR(i, cnt * cnt) {
+        const int a = i / cnt, b = i - a * cnt;
+        const int da = D.nz_dof[n0 + a], db = D.nz_dof[n0 + b];
+        if (da >= db) H[TRI(da) + db] += Dr * sm[L.tenJ + n0 + a] * sm[L.tenJ + n0 + b];
+      }
+    }
+  TSYNC();
+  if (nconT > 0) {   // tile-uniform
+    // weights in base-row space: W = sum_p D_p w_p w_p^T, w_p = e_n +- mu e_t; then U = W Jb per (contact, dof)
+    auto U = sm + L.conU;
+    for (int idx = t.tl; idx < nconT * nv; idx += nw) {
+      const int c = idx / nv, k = idx - c * nv;
+      auto cr = sm + L.con + 12 * c;
+      float Wnn = 0.f, Wnt[3] = {0.f, 0.f, 0.f}, Wtt[3] = {0.f, 0.f, 0.f};
+      int dim = 1;
+      if (c < ncon) {
+        const int adr = __float_as_int(cr[8]);
+        dim = __float_as_int(cr[9]);
+        if (adr >= 0) {
+          if (dim == 1) { if (EFC(E_JAR, adr) < 0.f) Wnn = EFC(E_D, adr); }
+          else
+            for (int q = 1; q < dim; q++) {
+              const int r0 = adr + 2 * (q - 1);
+              const float mu = EFC(E_COEF, r0);
+              const float Dp = EFC(E_JAR, r0) < 0.f ? EFC(E_D, r0) : 0.f, Dm = EFC(E_JAR, r0 + 1) < 0.f ? EFC(E_D, r0 + 1) : 0.f;
+              Wnn += Dp + Dm; Wnt[q - 1] = mu * (Dp - Dm); Wtt[q - 1] = mu * mu * (Dp + Dm);
+            }
+        }
+      }
+      auto J = sm + L.conJ + (c * nb) * nv + k; auto Uo = U + (c * nb) * nv + k;
+      const float jn = J[0];
+      float un = Wnn * jn;
+      for (int q = 1; q < nb; q++) {
+        const float jt = J[q * nv];
+        un = fmaf(Wnt[q - 1], jt, un);
+        Uo[q * nv] = fmaf(Wnt[q - 1], jn, Wtt[q - 1] * jt);
+      }
+      Uo[0] = un;
+    }
+    TSYNC();
+    const int nblk = (nv + 3) >> 2, nB = (nblk * (nblk + 1)) >> 1, nbase = nb * nconT;
+    for (int blk = t.tl; blk < nB; blk += nw) {
+      int R = 0, rem = blk;
+      while (rem > R) { rem -= R + 1; R++; }   // blk -> (R, C), C <= R
+      const int C = rem;
+      int ri[4], ci[4];
+#pragma unroll
+      for (int a = 0; a < 4; a++) { ri[a] = min(4 * R + a, nv - 1); ci[a] = min(4 * C + a, nv - 1); }
+      float acc[4][4];
+#pragma unroll
+      for (int a = 0; a < 4; a++)
+#pragma unroll
+        for (int b = 0; b < 4; b++) acc[a][b] = 0.f;
+      auto Ub = sm + L.conU; auto Jb = sm + L.conJ;
+      for (int i = 0; i < nbase; i++) {
+        float u[4], j[4];
+#pragma unroll
+        for (int a = 0; a < 4; a++) { u[a] = Ub[i * nv + ri[a]]; j[a] = Jb[i * nv + ci[a]]; }
+#pragma unroll
+        for (int a = 0; a < 4; a++)
+#pragma unroll
+          for (int b = 0; b < 4; b++) acc[a][b] = fmaf(u[a], j[b], acc[a][b]);
+      }
+#pragma unroll
+      for (int a = 0; a < 4; a++)
+#pragma unroll
+        for (int b = 0; b < 4; b++) {
+          const int r = 4 * R + a, c = 4 * C + b;
+          if (r < nv && c <= r) H[TRI(r) + c] += acc[a][b];
+        }
+    }
+    TSYNC();
+  }
+  // left-looking Cholesky, warps over rows; the diagonal of the factor goes to Hd (H keeps the unscaled pivot)
+  for (int j = 0; j < nv; j++) {
+    for (int r = j + t.tl; r < nv; r += nw) {
+      auto Hr = H + TRI(r); auto Hj = H + TRI(j);
+      float s0 = Hr[j], s1 = 0.f;
+      int k = 0;
+      for (; k + 1 < j; k += 2) { s0 = fmaf(-Hr[k], Hj[k], s0); s1 = fmaf(-Hr[k + 1], Hj[k + 1], s1); }
+      if (k < j) s0 = fmaf(-Hr[k], Hj[k], s0);
+      Hr[j] = s0 + s1;
+    }
+    TSYNC();
+    const float d = sqrtf(fmaxf(H[TRI(j) + j], MINVAL)), inv = 1.f / d;
+    for (int r = j + 1 + t.tl; r < nv; r += nw) H[TRI(r) + j] *= inv;
+    if (t.tl == 0) Hd[j] = d;
+    TSYNC();
+  }
+}
+// x <- (L L^T)^-1 x with the factor above; y is a scratch vector (one barrier per column each way)
+__device__ __noinline__ void cholSolveTile(int nv, SP H, SP Hd, SP x, SP y, Tm t) {
+  for (int j = 0; j < nv; j++) {
+    const float xj = x[j] / Hd[j];
+    if (t.tl == 0) y[j] = xj;
+    for (int r = j + 1 + t.tl; r < nv; r += t.nw) x[r] = fmaf(-H[TRI(r) + j], xj, x[r]);
+    TSYNC();
+  }
+  for (int j = nv - 1; j >= 0; j--) {
+    const float xj = y[j] / Hd[j];
+    if (t.tl == 0) x[j] = xj;
+    for (int r = t.tl; r < j; r += t.nw) y[r] = fmaf(-H[TRI(j) + r], xj, y[r]);
+    TSYNC();
+  }
+}
+// K points of the 1-D cost along the search direction in one pass over the lane's rows (see team.cu lsEval for `tol`)
+#ifndef LS_NOISE
+#define LS_NOISE 2e-6f
+#endif
+template <int K> __device__ __forceinline__ void lsEvalTile(int slot, SP sm, Tm t, int nefc, const float* a, const float* qg, float gtol, LsPt* out) {
+  const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
+  float q[4 * K];
+#pragma unroll
+  for (int i = 0; i < 4 * K; i++) q[i] = 0.f;
+  const int neq = D.neq;
+  for (int r = t.tl; r < nefc; r += t.nw) {
+    const float jar = EFC(E_JAR, r), jv = EFC(E_JV, r), Dr = EFC(E_D, r);
+#pragma unroll
+    for (int k = 0; k < K; k++) {
+      const float x = fmaf(a[k], jv, jar);
+      if (r < neq || x < 0.f) {   // equality rows come first and are always active
+        const float dj = Dr * jar;
+        q[4 * k] = fmaf(0.5f * dj, jar, q[4 * k]); q[4 * k + 1] = fmaf(dj, jv, q[4 * k + 1]);
+        q[4 * k + 2] = fmaf(0.5f * Dr * jv, jv, q[4 * k + 2]); q[4 * k + 3] = fmaf(fabsf(dj), fabsf(jv), q[4 * k + 3]);
+      }
+    }
+  }
+  tileSumN<4 * K>(t, q);
+#pragma unroll
+  for (int k = 0; k < K; k++) {
+    const float q0 = q[4 * k] + qg[0], q1 = q[4 * k + 1] + qg[1], q2 = q[4 * k + 2] + qg[2], qa = q[4 * k + 3] + fabsf(qg[1]);
+    LsPt p; p.alpha = a[k]; p.cost = a[k] * a[k] * q2 + a[k] * q1 + q0; p.d0 = 2.f * a[k] * q2 + q1; p.d1 = 2.f * q2;
+    p.tol = fmaxf(gtol, LS_NOISE * (qa + 2.f * fabsf(a[k]) * q2));
+    if (p.d1 <= 0.f) p.d1 = MINVAL;
+    out[k] = p;
+  }
+}
+
+struct NewtonMem { SP H, Hd, qacc, Ma, grad, search, Mv, tmp; };
+// mj_solNewton for the 32 worlds of the tile in lock step; returns the lane's iteration count
+__device__ __noinline__ int newtonTile(int slot, SP sm, Tm t, const NewtonMem& M, unsigned lmask, int ncon, int nconT, int nefc, int* status) {
+  const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
+  const int nv = D.nv, nw = t.nw;
+  SP qacc = M.qacc, Ma = M.Ma, grad = M.grad, search = M.search, Mv = M.Mv, tmp = M.tmp;
+  auto smooth = sm + L.smooth; auto qas = sm + L.qacc_smooth; auto warm = sm + L.warm;
+  const float scale = 1.f / (D.meaninertia * (float)max(1, nv));
+  // warm start: cheaper of qacc_warmstart and qacc_smooth
+  float costW = 3.4e38f;
+  if (!(D.disableflags & DSBL_WARMSTART)) {
+    mulMsparse(slot, sm + L.qM, warm, Ma, t);
+    TSYNC();
+    float g = 0.f;
+    TFOR(k, nv) g = fmaf(0.5f * (Ma[k] - smooth[k]), warm[k] - qas[k], g);
+    costW = TSUM(g) + residualCost(slot, sm, t, ncon, nefc, warm);
+  }
+  const float costS = residualCost(slot, sm, t, ncon, nefc, qas);
+  const bool useWarm = !(costW > costS);
+  TFOR(k, nv) qacc[k] = useWarm ? warm[k] : qas[k];
+  TSYNC();
+  mulMsparse(slot, sm + L.qM, qacc, Ma, t);
+  TSYNC();
+  float gauss = 0.f;
+  TFOR(k, nv) gauss = fmaf(0.5f * (Ma[k] - smooth[k]), qacc[k] - qas[k], gauss);
+  gauss = TSUM(gauss);
+  float cost = gauss + residualCost(slot, sm, t, ncon, nefc, qacc);
+  int iter = 0;
+  bool active = nefc > 0;
+  const int lsmax = D.ls_iterations;
+  for (;;) {
+    // gradient and termination tests
+    constraintForce(slot, sm, t, ncon, nefc, tmp);
+    float gg[2] = {0.f, 0.f};
+    TFOR(k, nv) {
+      const float g = Ma[k] - smooth[k] - tmp[k]; grad[k] = g; search[k] = g; gg[0] = fmaf(g, g, gg[0]);
+      const float a = fabsf(Ma[k]) + fabsf(smooth[k]) + fabsf(tmp[k]); gg[1] = fmaf(a, a, gg[1]);
+    }
+    tileSumN<2>(t, gg);
+    const float gn = sqrtf(gg[0]), gr = sqrtf(gg[1]);
+    // MuJoCo's test (scaled gradient < tolerance = 1e-8) cannot be met in float32: the gradient is a difference of
+    // O(gr) terms and bottoms out near eps * gr, after which further iterations only chase rounding noise.
+    if (active && iter > 0 && (scale * gn < D.tolerance || gn < GRAD_NOISE * gr)) active = false;
+    if (active && iter >= D.iterations) { *status |= MYO_WORLD_SOLVER_MAXITER; active = false; }
+    if (!__ballot_sync(lmask, active)) break;   // the tile is done when its slowest world is
+    hessianTile(slot, sm, t, M.H, M.Hd, ncon, nconT, nefc);
+    cholSolveTile(nv, M.H, M.Hd, search, tmp, t);
+    float sn = 0.f;
+    TFOR(k, nv) { const float s = -search[k]; search[k] = s; sn = fmaf(s, s, sn); }
+    sn = sqrtf(TSUM(sn));
+    if (active && !(sn >= MINVAL)) active = false;
+    // exact line search along `search`
+    mulMsparse(slot, sm + L.qM, search, Mv, t);
+    auto bx = sm + L.basev;
+    baseMul(slot, sm, t, ncon, search, bx);
+    TSYNC();
+    for (int r = t.tl; r < nefc; r += nw) EFC(E_JV, r) = rowMul(slot, sm, r, search, bx);
+    float g12[2] = {0.f, 0.f};
+    TFOR(k, nv) { g12[0] = fmaf(search[k], Ma[k] - smooth[k], g12[0]); g12[1] = fmaf(0.5f * search[k], Mv[k], g12[1]); }
+    tileSumN<2>(t, g12);   // its barriers also publish E_JV
+    const float qg[3] = {gauss, g12[0], g12[1]};
+    const float gtol = D.tolerance * D.ls_tolerance * sn / scale;
+    int lsiter = 0;
+    LsPt p0, p1;
+    { const float a0 = 0.f; lsEvalTile<1>(slot, sm, t, nefc, &a0, qg, gtol, &p0); lsiter++; }
+    { const float a1 = p0.alpha - p0.d0 / p0.d1; lsEvalTile<1>(slot, sm, t, nefc, &a1, qg, gtol, &p1); lsiter++; }
+    if (p0.cost < p1.cost) p1 = p0;
+    bool done = !active || fabsf(p1.d0) < p1.tol;
+    const float dir = p1.d0 < 0.f ? 1.f : -1.f;
+    LsPt p2 = p1; bool have2 = false;
+    for (;;) {   // Newton steps on the 1-D cost until the derivative changes sign
+      const bool want = !done && p1.d0 * dir <= -p1.tol && lsiter < lsmax;
+      if (!__ballot_sync(lmask, want)) break;
+      const float a = want ? p1.alpha - p1.d0 / p1.d1 : 0.f;
+      LsPt pn; lsEvalTile<1>(slot, sm, t, nefc, &a, qg, gtol, &pn);
+      if (want) { p2 = p1; have2 = true; p1 = pn; lsiter++; if (fabsf(p1.d0) < p1.tol) done = true; }
+    }
+    bool refine = !done && lsiter < lsmax && have2;
+    LsPt lo = p2, hi = p1;
+    for (;;) {   // bracket refinement: Newton steps from both ends and the midpoint, three points per pass
+      const bool want = refine && lsiter < lsmax;
+      if (!__ballot_sync(lmask, want)) break;
+      const float ca[3] = {want ? lo.alpha - lo.d0 / lo.d1 : 0.f, want ? hi.alpha - hi.d0 / hi.d1 : 0.f, want ? 0.5f * (lo.alpha + hi.alpha) : 0.f};
+      LsPt cand[3];
+      lsEvalTile<3>(slot, sm, t, nefc, ca, qg, gtol, cand);
+      if (want) {
+        lsiter += 3;
+        bool moved = false, hit = false;
+        LsPt best = lo.cost < hi.cost ? lo : hi;
+#pragma unroll
+        for (int q = 0; q < 3; q++) {
+          if (hit) continue;
+          const LsPt c = cand[q];
+          if (fabsf(c.d0) < c.tol) { p1 = c; hit = true; continue; }
+          if (!((c.alpha - lo.alpha) * dir > 0.f && (hi.alpha - c.alpha) * dir > 0.f)) continue;
+          if (c.d0 * dir < 0.f) lo = c; else hi = c;
+          moved = true;
+          if (c.cost < best.cost) best = c;
+        }
+        if (hit) { done = true; refine = false; }
+        else if (!moved) { p1 = best; refine = false; }
+        else p1 = lo.cost < hi.cost ? lo : hi;
+      }
+    }
+    const float alpha = p1.alpha;
+    if (active && alpha == 0.f) active = false;
+    if (active) TFOR(k, nv) { qacc[k] = fmaf(alpha, search[k], qacc[k]); Ma[k] = fmaf(alpha, Mv[k], Ma[k]); }
+    float gc[2] = {0.f, 0.f};
+    for (int r = t.tl; r < nefc; r += nw) {
+      float jar = EFC(E_JAR, r);
+      if (active) { jar = fmaf(alpha, EFC(E_JV, r), jar); EFC(E_JAR, r) = jar; }
+      if (rowOn(EFCI(E_DESC0, r), jar)) gc[1] = fmaf(0.5f * EFC(E_D, r) * jar, jar, gc[1]);
+    }
+    TSYNC();
+    TFOR(k, nv) gc[0] = fmaf(0.5f * (Ma[k] - smooth[k]), qacc[k] - qas[k], gc[0]);
+    tileSumN<2>(t, gc);
+    if (active) {
+      gauss = gc[0];
+      const float newcost = gauss + gc[1];
+      iter++;
+      const float improvement = scale * (cost - newcost);
+      cost = newcost;
+      if (improvement < D.tolerance) active = false;
+    }
+  }
+  constraintForce(slot, sm, t, ncon, nefc, sm + L.qfrc_con);
+  return iter;
+}
+
+// Shared memory of a tile: Hessian (lower triangle), its factor's diagonal and six nv-vectors, [element][32 lanes].  When a
+// model's block does not fit (nv beyond ~55), the same kernel runs with everything in the world's scratch column.
+static inline size_t newtonSmemFloats(int nv) { return (size_t)(TRI(nv) + 7 * nv) * 32; }
+#define NEWTON_SMEM_MAX (200 * 1024)
+__global__ void __launch_bounds__(512) newtonKernel(int slot, int fslot, int nworld, int stride, const int* __restrict__ mask, int check_acc,
+                                                    int use_smem, float* __restrict__ scratch) {
+  const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
+  extern __shared__ float tileShared[];
+  __shared__ int sBad[32];
+  const int lane = threadIdx.x & 31;
+  Ctx c = tileCtx(nworld, stride, mask, scratch);
+  const unsigned lmask = __ballot_sync(0xffffffffu, c.live);
+  if (!c.live) return;
+  SP sm = c.sm; Tm t = c.t;
+  const int nv = D.nv;
+  int status = __float_as_int(sm[L.wstate + WS_STATUS]);
+  const int ncon = __float_as_int(sm[L.counts]);
+  const int nconT = __reduce_max_sync(lmask, ncon);
+  if (t.tl == 0) sBad[lane] = 0;
+  int nefc = makeConstraintTile(slot, sm, t, ncon, nconT, &status);
+  const int nefcT = __reduce_max_sync(lmask, nefc);
+  int niter = 0;
+  if (nefcT == 0) {   // tile-uniform
+    TFOR(i, nv) { const float a = sm[L.qacc_smooth + i]; sm[L.qacc + i] = a; sm[L.warm + i] = a; sm[L.qfrc_con + i] = 0.f; }
+  } else {
+    NewtonMem M;
+    if (use_smem) {
+      float* p = tileShared + lane;
+      auto take = [&](int n) { SP r; r.p = p; r.s = 32; p += n * 32; return r; };
+      M.H = take(TRI(nv)); M.Hd = take(nv); M.qacc = take(nv); M.Ma = take(nv); M.grad = take(nv); M.search = take(nv); M.Mv = take(nv); M.tmp = take(nv);
+    } else {
+      M.H = sm + L.H; M.Hd = sm + L.H + TRI(nv); M.qacc = sm + L.nvec; M.Ma = M.qacc + nv; M.grad = M.Ma + nv; M.search = M.grad + nv;
+      M.Mv = M.search + nv; M.tmp = M.Mv + nv;
+    }
+    niter = newtonTile(slot, sm, t, M, lmask, ncon, nconT, nefc, &status);
+    // a world without rows in a tile that has some: its warm start and its only candidate coincide, qacc = qacc_smooth
+    TFOR(i, nv) { const float a = nefc > 0 ? M.qacc[i] : sm[L.qacc_smooth + i]; sm[L.qacc + i] = a; sm[L.warm + i] = a; if (nefc == 0) sm[L.qfrc_con + i] = 0.f; }
+  }
+  TSYNC();
+  // mj_checkAcc: a world whose qacc went bad is reset (qpos0, zero velocity / activation) and flagged; finishKernel does
+  // not integrate it, its next forward pass starts from the reset state.
+  int skip = 0;
+  if (check_acc) {
+    bool bad = false;
+    TFOR(i, nv) bad |= !(fabsf(sm[L.qacc + i]) < 1e10f);
+    if (bad) sBad[lane] = 1;
+    TSYNC();
+    if (sBad[lane]) {
+      TFOR(i, D.nq) sm[L.qpos + i] = D.qpos0[i];
+      TFOR(i, nv) { sm[L.qvel + i] = 0.f; sm[L.warm + i] = 0.f; }
+      TFOR(i, D.na) sm[L.act + i] = 0.f;
+      status |= MYO_WORLD_BADQACC; skip = 1;
+    }
+  }
+  if (fslot != MYO_NSLOT && D.nsensor > 0) touchSensors(slot, fslot, sm, t, c.W, nefc > 0 ? ncon : 0);
+  if (t.tl == 0) {
+    sm[L.counts + 1] = __int_as_float(nefc); sm[L.counts + 2] = __int_as_float(niter);
+    sm[L.wstate + WS_STATUS] = __int_as_float(status); sm[L.wstate + WS_SKIP] = __int_as_float(skip);
   }
 }
 
@@ -365,7 +903,7 @@ static int envInt(const char* name, int dflt) { const char* e = getenv(name); re
 int myo_tile_launch(int kernel, int slot, int fslot, int nworld, int stride, const int* mask, int flags, float* scratch, void* stream) {
   static const int nwKin = envInt("MYO_NW_KIN", 16), nwTen = envInt("MYO_NW_TEN", 16), nwIne = envInt("MYO_NW_INE", 8),
                    nwCol = envInt("MYO_NW_COL", 16), nwVel = envInt("MYO_NW_VEL", 8), nwFin = envInt("MYO_NW_FIN", 8),
-                   nwOut = envInt("MYO_NW_OUT", 8), yOut = envInt("MYO_Y_OUT", 4);
+                   nwOut = envInt("MYO_NW_OUT", 8), yOut = envInt("MYO_Y_OUT", 4), nwNew = envInt("MYO_NW_NEWTON", 8);
   const int tiles = (nworld + 31) / 32;
   cudaStream_t st = (cudaStream_t)stream;
   switch (kernel) {
@@ -375,6 +913,22 @@ int myo_tile_launch(int kernel, int slot, int fslot, int nworld, int stride, con
     case MYO_K_COLLIDE: collideKernel<<<tiles, 32 * nwCol, 0, st>>>(slot, nworld, stride, mask, scratch); break;
     case MYO_K_VELACT: velactKernel<<<tiles, 32 * nwVel, 0, st>>>(slot, fslot, nworld, stride, mask, flags, scratch); break;
     case MYO_K_FINISH: finishKernel<<<tiles, 32 * nwFin, 0, st>>>(slot, fslot, nworld, stride, mask, flags, scratch); break;
+    case MYO_K_NEWTON: {
+      const int nv = flags >> 8;   // the host passes nv in the upper bits (the model lives in constant memory)
+      size_t shmem = newtonSmemFloats(nv) * sizeof(float);
+      const int use_smem = shmem <= NEWTON_SMEM_MAX ? 1 : 0;
+      if (!use_smem) shmem = 0;
+      static bool configured[64] = {false};
+      int dev = 0;
+      if (shmem > 48 * 1024) {
+        if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return -1;
+        if (!configured[dev]) {
+          if (cudaFuncSetAttribute(newtonKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, NEWTON_SMEM_MAX) != cudaSuccess) return -1;
+          configured[dev] = true;
+        }
+      }
+      newtonKernel<<<tiles, 32 * nwNew, shmem, st>>>(slot, fslot, nworld, stride, mask, flags & 1, use_smem, scratch);
+    } break;
     case MYO_K_CONOUT: conoutKernel<<<dim3(tiles, yOut), 32 * nwOut, 0, st>>>(slot, fslot, nworld, stride, mask, scratch); break;
     default: return -1;
   }

@@ -121,20 +121,14 @@ def test_factor_and_constraint_forces(rows, models, name):
 
 @pytest.mark.parametrize("name", ["hand", "legs"])
 def test_solver_iterations_close_to_oracle(rows, models, name):
-    """solver_niter: float32 stops on its noise floors (GRAD_NOISE / LS_NOISE), the float64 oracle on MuJoCo's
-    tolerance, so counts may differ by an iteration; the float32 build of the oracle is the like-for-like yardstick."""
+    """solver_niter against the float64 oracle: float32 stops on its noise floors (GRAD_NOISE / LS_NOISE)
+    where float64 stops on MuJoCo's tolerance, so a count may differ by one iteration (measured: MyoHand identical in 32 of
+    32 worlds, legs within one; the oracle's own float32 build needs one MORE iteration than either in most worlds)."""
     m, ref, got = rows(name)
-    nw = len(ref)
-    qpos, qvel, act, ctrl = parity.random_state(m, nw, 1234, qpos_spread=0.9)
-    import oracle
-    o = oracle.Oracle(m, use_float=True)
-    n32 = []
-    for w in range(nw):
-        o.set_state(qpos[w], qvel[w], act[w], ctrl[w], np.zeros(m.nv)); o.forward(); n32.append(int(o.solver_niter[0]))
     g = got.solver_niter[:, 0]
     n64 = np.array([int(r["solver_niter"][0]) for r in ref])
     assert np.all((g > 0) == (n64 > 0)), "a world solved without rows, or skipped the solve with rows"
-    assert np.abs(g - np.array(n32)).max() <= 2 and np.mean(g == np.array(n32)) >= 0.5, f"gpu {g} f32 oracle {n32} f64 oracle {n64}"
+    assert np.abs(g - n64).max() <= 1 and np.mean(g == n64) >= 0.5, f"gpu {g} f64 oracle {n64}"
 
 
 def test_benchmarked_shape_matches_oracle(models):
