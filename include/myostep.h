@@ -192,9 +192,9 @@ void myo_batch_destroy(myo_batch *b);
 int myo_batch_nconmax(const myo_batch *b);
 int myo_batch_njmax(const myo_batch *b);
 int myo_batch_smem_bytes(const myo_batch *b);   /* bytes of per-world scratch in the library-owned global buffer */
-int myo_batch_team(const myo_batch *b);         /* lanes per world of the TEAM-mode kernels (constraint rows, Newton) picked for this batch (4, 8 or 16) */
-int myo_batch_ctas_per_sm(const myo_batch *b);  /* always 1 (kept for ABI stability: round 1 had a two-CTAs-per-SM build of the one-launch kernel) */
-int myo_batch_engine(const myo_batch *b);       /* 1: phase pipeline (lane = world kernels + team solver, the default); 0: one-launch kernel (MYO_ENGINE=mono) */
+int myo_batch_team(const myo_batch *b);         /* lanes per world: always 1 (lane = world; the warps of a tile CTA share the items) */
+int myo_batch_ctas_per_sm(const myo_batch *b);  /* always 1 (kept for ABI stability with round 1) */
+int myo_batch_engine(const myo_batch *b);       /* always 1: the phase pipeline of lane = world kernels (round 1's one-launch kernel, 0, is gone) */
 
 /* Per-world element count / element size of a field for this batch (0 elements = field absent for the model). */
 int64_t myo_field_count(const myo_batch *b, int field);
@@ -227,13 +227,9 @@ int myo_forward_posvel(myo_batch *b, const int32_t *world_mask_dev, void *cuda_s
  * Output fields describe the last substep's forward pass, as mjData does after mj_step. */
 int myo_step(myo_batch *b, int nsubsteps, void *cuda_stream);
 
-/* Pipelined wide outputs (opt-in, for rollouts that do not read the full mjData after every step): with `on`, the
- * wide-output kernel of a full unmasked myo_step / myo_step_host (site / geom / body poses, dense ten_J, actuator_moment,
- * qM, efc_J, contact_* ..., see csrc/out.cu) is enqueued on a library-owned side stream and runs under the NEXT step's
- * kernel (the step alternates between two scratch buffers).  State fields and every field the step kernel writes itself
- * keep the caller's stream order; the wide fields of the last step are complete on `cuda_stream` after
- * myo_outputs_join, which every other entry point (forward, reset, masked / posvel passes, env steps) calls itself.
- * Off (the default): mjx.step semantics, every field is complete in stream order when myo_step returns. */
+/* Kept for ABI stability with round 1 (whose separate wide-output kernel could be pipelined under the next step): every
+ * field is now written, as full lines, by the pipeline phase that produces it, and is complete in stream order when
+ * myo_step returns (mjx.step semantics).  Both calls are accepted and do nothing. */
 int myo_batch_set_pipelined(myo_batch *b, int on);
 int myo_outputs_join(myo_batch *b, void *cuda_stream);
 

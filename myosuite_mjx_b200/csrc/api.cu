@@ -13,22 +13,7 @@
 
 
 namespace {
-const TeamVariant kVariants[] = {{4, myo_team_upload_4, myo_team_launch_4, myo_team_solve_4},
-                                 {8, myo_team_upload_8, myo_team_launch_8, myo_team_solve_8},
-                                 {16, myo_team_upload_16, myo_team_launch_16, myo_team_solve_16}};
 int64_t g_launches = 0;
-// Engine: the phase pipeline (tile.cu lane = world kernels + team.cu solveKernel) unless MYO_ENGINE=mono asks for the
-// round-1 whole-step kernel.  Lanes per world of the TEAM-mode kernels: 8 (the solver's loops -- ~65 rows, 23 dofs, ~13
-// contacts per MyoHand world -- keep 8 lanes busy; 16 lanes idle half of them); the one-launch kernel takes 16 when all of
-// its warps are resident at once (small batches).  MYO_TEAM overrides (developer knob).
-bool pickMono() { const char* e = getenv("MYO_ENGINE"); return e && std::string(e) == "mono"; }
-const TeamVariant* pickVariant(int nworld, bool mono) {
-  int team = 8;
-  if (mono && (int64_t)nworld * 16 <= (int64_t)148 * 14 * 32) team = 16;
-  if (const char* e = getenv("MYO_TEAM")) team = atoi(e);
-  for (const TeamVariant& v : kVariants) if (v.team == team) return &v;
-  return &kVariants[1];
-}
 thread_local std::string g_err;
 bool g_slot_used[64] = {false};
 int fail(int code, const std::string& msg) { g_err = msg; return code; }
@@ -151,15 +136,11 @@ int myo_batch_create(const myo_model* m, int nworld, int nconmax, int njmax, myo
   } catch (const std::string& e) { g_slot_used[b->slot] = false; delete b; return fail(MYO_ERR_ARG, e); }
   {
     void* p = nullptr;
-    b->mono = pickMono();
-    b->kern = pickVariant(nworld, b->mono);
-    b->stride = (nworld + 31) & ~31;
-    // scratch element k of world w lives at k * stride + w: the kernels form that index in 32 bits
-    if ((int64_t)b->L.total * b->stride >= ((int64_t)1 << 31)) { g_slot_used[b->slot] = false; delete b; return fail(MYO_ERR_ARG, "batch too large: per-world scratch x worlds exceeds 2^31 floats"); }
-    const size_t bytes = (size_t)b->L.total * b->stride * sizeof(float);
-    // zeroed once: a record the kernels have not written yet (rows past an overflow, lanes of a partial tile) reads as zeros
+    // tile-blocked scratch [tiles][L.total][32]; zeroed once: a record the kernels have not written yet (rows past an
+    // overflow, lanes of a partial tile) reads as zeros
+    const size_t bytes = (size_t)((nworld + 31) / 32) * b->L.total * 32 * sizeof(float);
     if (cudaMalloc(&p, bytes) != cudaSuccess || cudaMemset(p, 0, bytes) != cudaSuccess) { g_slot_used[b->slot] = false; delete b; return fail(MYO_ERR_CUDA, "cudaMalloc of the per-world scratch failed"); }
-    b->owned.push_back(p); b->scratch = (float*)p; b->scratch_buf[0] = b->scratch;
+    b->owned.push_back(p); b->scratch = (float*)p;
   }
   // library-owned default state buffers (bind overrides them)
   for (int f : kStateFields) {
@@ -175,17 +156,15 @@ void myo_batch_destroy(myo_batch* b) {
   if (!b) return;
   cudaSetDevice(b->model->device);
   for (void* p : b->owned) cudaFree(p);
-  for (int i = 0; i < 2; i++) if (b->ev_out[i]) { cudaEventSynchronize((cudaEvent_t)b->ev_out[i]); cudaEventDestroy((cudaEvent_t)b->ev_out[i]); }
-  if (b->copy_stream) { cudaStreamSynchronize((cudaStream_t)b->copy_stream); cudaStreamDestroy((cudaStream_t)b->copy_stream); cudaEventDestroy((cudaEvent_t)b->ev_step); cudaEventDestroy((cudaEvent_t)b->ev_copy); }
   if (b->slot >= 0) g_slot_used[b->slot] = false;
   delete b;
 }
 int myo_batch_nconmax(const myo_batch* b) { return b ? b->D.nconmax : 0; }
 int myo_batch_njmax(const myo_batch* b) { return b ? b->D.njmax : 0; }
 int myo_batch_smem_bytes(const myo_batch* b) { return b ? b->L.total * 4 : 0; }
-int myo_batch_team(const myo_batch* b) { return b ? b->kern->team : 0; }
+int myo_batch_team(const myo_batch* b) { return b ? 1 : 0; }
 int myo_batch_ctas_per_sm(const myo_batch* b) { return b ? 1 : 0; }
-int myo_batch_engine(const myo_batch* b) { return b ? (b->mono ? 0 : 1) : -1; }
+int myo_batch_engine(const myo_batch* b) { return b ? 1 : -1; }
 int64_t myo_field_count(const myo_batch* b, int field) { return (b && field >= 0 && field < MYO_F_COUNT) ? fieldCount(b->D, field) : 0; }
 
 int myo_batch_bind(myo_batch* b, int field, void* dev_ptr, int64_t nbytes) {
@@ -199,26 +178,8 @@ int myo_batch_bind(myo_batch* b, int field, void* dev_ptr, int64_t nbytes) {
     for (int f : kStateFields) if (f == field) return fail(MYO_ERR_ARG, "state fields cannot be unbound");
   }
   if (b->F.p[field] == dev_ptr) return MYO_OK;   // re-binding the same buffer (a caller that binds on every call) changes nothing
-  if (b->out_pending) { cudaEventSynchronize((cudaEvent_t)b->ev_out[b->cur]); b->out_pending = false; }   // a running output kernel still writes the old buffers
   b->F.p[field] = dev_ptr;
   b->dirty = true;
-  return MYO_OK;
-}
-
-static int ensureSide(myo_batch* b) {
-  if (b->copy_stream) return MYO_OK;
-  cudaStream_t cs; cudaEvent_t e0, e1;
-  if (cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking) != cudaSuccess || cudaEventCreateWithFlags(&e0, cudaEventDisableTiming) != cudaSuccess ||
-      cudaEventCreateWithFlags(&e1, cudaEventDisableTiming) != cudaSuccess)
-    return fail(MYO_ERR_CUDA, "side stream creation failed");
-  b->copy_stream = cs; b->ev_step = e0; b->ev_copy = e1;
-  return MYO_OK;
-}
-// the caller's stream waits for a pipelined output kernel that may still be running
-static int joinOutputs(myo_batch* b, void* stream) {
-  if (!b->out_pending) return MYO_OK;
-  if (cudaStreamWaitEvent((cudaStream_t)stream, (cudaEvent_t)b->ev_out[b->cur], 0) != cudaSuccess) return fail(MYO_ERR_CUDA, "joining the output kernel failed");
-  b->out_pending = false;
   return MYO_OK;
 }
 
@@ -236,47 +197,54 @@ static int clearPathPoints(myo_batch* b, void* stream) {
   return MYO_OK;
 }
 
-// The phase pipeline: one mj_step = kin -> tendon -> inertia -> collide -> velact (tile.cu, lane = world) -> solve (team.cu,
-// 8 lanes per world) -> conout -> finish (tile.cu).  All launches go to the caller's stream, in order; every mjData field
-// is written by the phase that produces it, as full lines; inner substeps of a fused launch materialise nothing.
+// The phase pipeline: one mj_step = kin -> tendon -> inertia -> collide -> velact -> newton -> conout -> finish (tile.cu, lane =
+// world).  All launches go to the caller's stream, in order; every mjData field is written by the phase that produces it,
+// as full lines; inner substeps of a fused launch materialise nothing.
 static int launchPhases(myo_batch* b, int nsub, int forward_only, const int32_t* mask, int do_reset, void* stream) {
   int rc;
   if (b->dirty) {
-    if (myo_tile_upload(b->slot, b->D, b->L, b->F, stream) != 0 || b->kern->upload(b->slot, b->D, b->L, b->F, stream) != 0)
-      return fail(MYO_ERR_CUDA, "parameter upload failed");
+    if (myo_tile_upload(b->slot, b->D, b->L, b->F, stream) != 0) return fail(MYO_ERR_CUDA, "parameter upload failed");
     static const int conFields[] = {MYO_F_NCON, MYO_F_NEFC, MYO_F_SOLVER_NITER, MYO_F_CONTACT_GEOM, MYO_F_CONTACT_DIM, MYO_F_CONTACT_EFC_ADDRESS,
                                     MYO_F_CONTACT_DIST, MYO_F_CONTACT_POS, MYO_F_CONTACT_FRAME, MYO_F_CONTACT_INCLUDEMARGIN, MYO_F_CONTACT_FRICTION,
                                     MYO_F_CONTACT_SOLREF, MYO_F_CONTACT_SOLIMP, MYO_F_EFC_J, MYO_F_EFC_POS, MYO_F_EFC_MARGIN, MYO_F_EFC_D,
                                     MYO_F_EFC_AREF, MYO_F_EFC_FORCE, MYO_F_EFC_TYPE};
-    b->wide = false;   // here: some contact / constraint record field is bound, conoutKernel runs
-    for (int f : conFields) b->wide |= b->F.p[f] != nullptr;
+    b->conout = false;
+    for (int f : conFields) b->conout |= b->F.p[f] != nullptr;
     if ((rc = clearPathPoints(b, stream)) != MYO_OK) return rc;
     b->dirty = false;
   }
   const bool posvel = forward_only == 2;
   const int nloop = forward_only ? 1 : nsub;
-  const int slot = b->slot, nw = b->nworld, st = b->stride;
+  const int slot = b->slot, nw = b->nworld;
   float* scr = b->scratch;
+  static const bool debug_sync = getenv("MYO_DEBUG_SYNC") != nullptr;   // developer knob: synchronise after every kernel and name the one that failed
   auto tile = [&](int k, int fslot, int flags) {
     g_launches++;
-    return myo_tile_launch(k, slot, fslot, nw, st, mask, flags, scr, stream);
+    int r = myo_tile_launch(k, slot, fslot, nw, mask, flags, scr, stream);
+    if (debug_sync && r == 0) {
+      const cudaError_t e = cudaStreamSynchronize((cudaStream_t)stream);
+      if (e != cudaSuccess) { fprintf(stderr, "[myostep] tile kernel %d failed: %s\n", k, cudaGetErrorString(e)); r = -1; }
+    }
+    return r;
   };
   bool ok = true;
+  static const int debug_stop = getenv("MYO_DEBUG_STOP") ? atoi(getenv("MYO_DEBUG_STOP")) : -1;   // developer knob: end the pipeline after this many kernels
+  int nk = 0;
+#define STOP_HERE() if (debug_stop >= 0 && ++nk >= debug_stop) break
   for (int sub = 0; sub < nloop && ok; sub++) {
     const bool first = sub == 0, last = sub == nloop - 1;
     const int fslot = last ? slot : MYO_PARAM_SLOTS;   // slot MYO_PARAM_SLOTS: no field bound, "materialise nothing"
-    ok &= tile(MYO_K_KIN, fslot, (first ? (do_reset ? MYO_KIN_RESET : MYO_KIN_LOAD) : 0) | (forward_only ? 0 : MYO_KIN_CHECK)) == 0;
-    ok &= tile(MYO_K_TENDON, fslot, 0) == 0;
+    ok &= tile(MYO_K_KIN, fslot, (first ? (do_reset ? MYO_KIN_RESET : MYO_KIN_LOAD) : 0) | (forward_only ? 0 : MYO_KIN_CHECK)) == 0; STOP_HERE();
+    ok &= tile(MYO_K_TENDON, fslot, 0) == 0; STOP_HERE();
     if (!posvel) {
-      ok &= tile(MYO_K_INERTIA, fslot, forward_only ? 0 : 1) == 0;
-      ok &= tile(MYO_K_COLLIDE, fslot, 0) == 0;
+      ok &= tile(MYO_K_INERTIA, fslot, forward_only ? 0 : 1) == 0; STOP_HERE();
+      ok &= tile(MYO_K_COLLIDE, fslot, 0) == 0; STOP_HERE();
     }
-    ok &= tile(MYO_K_VELACT, fslot, posvel ? 1 : 0) == 0;
+    ok &= tile(MYO_K_VELACT, fslot, posvel ? 1 : 0) == 0; STOP_HERE();
     if (posvel) break;
-    static const bool team_solver = getenv("MYO_SOLVER") && std::string(getenv("MYO_SOLVER")) == "team";   // developer knob: the TEAM-mode solver
-    if (team_solver) { g_launches++; ok &= b->kern->solve(slot, fslot, b->L, nw, st, mask, forward_only ? 0 : 1, scr, stream) == 0; }
-    else ok &= tile(MYO_K_NEWTON, fslot, (forward_only ? 0 : 1) | (b->D.nv << 8)) == 0;
-    if (last && b->wide) ok &= tile(MYO_K_CONOUT, fslot, 0) == 0;
+    ok &= tile(MYO_K_NEWTON, fslot, (forward_only ? 0 : 1) | (b->D.nv << 8)) == 0;
+    STOP_HERE();
+    if (last && b->conout) { ok &= tile(MYO_K_CONOUT, fslot, 0) == 0; STOP_HERE(); }
     ok &= tile(MYO_K_FINISH, fslot, (forward_only ? 0 : MYO_FIN_EULER) | (last && (!forward_only || do_reset) ? MYO_FIN_STATE : 0) |
                                         (last ? MYO_FIN_WARM | MYO_FIN_ACC : 0)) == 0;
   }
@@ -284,79 +252,15 @@ static int launchPhases(myo_batch* b, int nsub, int forward_only, const int32_t*
   return MYO_OK;
 }
 
-static int launch(myo_batch* b, int nsub, int forward_only, const int32_t* mask, int do_reset, void* stream, cudaEvent_t after_step = nullptr) {
+static int launch(myo_batch* b, int nsub, int forward_only, const int32_t* mask, int do_reset, void* stream) {
   int rc = checkReady(b);
   if (rc) return rc;
-  if (!b->mono) {
-    if ((rc = launchPhases(b, nsub, forward_only, mask, do_reset, stream)) != MYO_OK) return rc;
-    if (after_step && cudaEventRecord(after_step, (cudaStream_t)stream) != cudaSuccess) return fail(MYO_ERR_CUDA, "event record failed");
-    return MYO_OK;
-  }
-  if (b->dirty) {
-    // wide outputs (out.cu) are written by the second kernel; the step kernel sees null pointers for them
-    static const bool wide_on = !(getenv("MYO_WIDE_OUT") && atoi(getenv("MYO_WIDE_OUT")) == 0);
-    FieldPtrs Fstep = b->F;
-    b->wide = false;
-    if (wide_on)
-      for (int i = 0; i < kNumWideOutFields; i++)
-        if (b->F.p[kWideOutFields[i]]) { Fstep.p[kWideOutFields[i]] = nullptr; b->wide = true; }
-    SmemLayout Ls = b->L;
-    Ls.wantw = b->F.p[MYO_F_WRAP_XPOS] || b->F.p[MYO_F_WRAP_OBJ] || b->F.p[MYO_F_TEN_WRAPADR] || b->F.p[MYO_F_TEN_WRAPNUM];
-    if (b->kern->upload(b->slot, b->D, Ls, Fstep, stream) != 0) return fail(MYO_ERR_CUDA, "parameter upload failed");
-    if (b->wide && myo_out_upload(b->slot, b->D, b->L, b->F, stream) != 0) return fail(MYO_ERR_CUDA, "parameter upload failed");
-    if ((rc = clearPathPoints(b, stream)) != MYO_OK) return rc;
-    b->dirty = false;
-  }
-  // A full, unmasked step of a pipelined batch with wide outputs: its output kernel goes to the side stream and the step
-  // runs on the other scratch buffer, so the NEXT step's kernel does not wait for it.  Every other launch joins first
-  // and works on the buffer of the last pass (posvel / masked passes read what that pass left).
-  const bool pipe = b->pipelined && b->wide && !forward_only && !mask && !do_reset;
-  if (pipe) {
-    const int nxt = b->cur ^ 1;
-    if ((rc = ensureSide(b)) != MYO_OK) return rc;
-    if (!b->scratch_buf[nxt]) {
-      void* p = nullptr;
-      const size_t bytes = (size_t)b->L.total * b->stride * sizeof(float);
-      if (cudaMalloc(&p, bytes) != cudaSuccess || cudaMemset(p, 0, bytes) != cudaSuccess) return fail(MYO_ERR_CUDA, "cudaMalloc of the second scratch buffer failed");
-      b->owned.push_back(p); b->scratch_buf[nxt] = (float*)p;
-    }
-    for (int i = 0; i < 2; i++)
-      if (!b->ev_out[i]) { cudaEvent_t e; if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess) return fail(MYO_ERR_CUDA, "event creation failed"); b->ev_out[i] = e; }
-    // the output kernel that last read buffer `nxt` (two steps ago) must be done before this step overwrites it
-    if (b->ev_out_set[nxt] && cudaStreamWaitEvent((cudaStream_t)stream, (cudaEvent_t)b->ev_out[nxt], 0) != cudaSuccess) return fail(MYO_ERR_CUDA, "stream wait failed");
-    b->cur = nxt;
-  } else if ((rc = joinOutputs(b, stream)) != MYO_OK) return rc;
-  b->scratch = b->scratch_buf[b->cur];
-  g_launches++;
-  if (b->kern->launch(b->slot, b->L, b->nworld, b->stride, nsub, forward_only, mask, do_reset, b->scratch, stream) != 0)
-    return fail(MYO_ERR_CUDA, std::string("kernel launch failed: ") + cudaGetErrorString(cudaGetLastError()));
-  if (pipe) after_step = (cudaEvent_t)b->ev_step;
-  if (after_step && cudaEventRecord(after_step, (cudaStream_t)stream) != cudaSuccess) return fail(MYO_ERR_CUDA, "event record failed");
-  if (b->wide) {
-    g_launches++;
-    cudaStream_t os = (cudaStream_t)stream;
-    if (pipe) {
-      os = (cudaStream_t)b->copy_stream;
-      if (cudaStreamWaitEvent(os, (cudaEvent_t)b->ev_step, 0) != cudaSuccess) return fail(MYO_ERR_CUDA, "stream wait failed");
-    }
-    if (myo_out_launch(b->slot, b->nworld, b->stride, mask, forward_only == 2, b->scratch, os) != 0)
-      return fail(MYO_ERR_CUDA, std::string("kernel launch failed: ") + cudaGetErrorString(cudaGetLastError()));
-    if (pipe) {
-      if (cudaEventRecord((cudaEvent_t)b->ev_out[b->cur], os) != cudaSuccess) return fail(MYO_ERR_CUDA, "event record failed");
-      b->ev_out_set[b->cur] = true; b->out_pending = true;
-    }
-  }
-  return MYO_OK;
+  return launchPhases(b, nsub, forward_only, mask, do_reset, stream);
 }
-int myo_batch_set_pipelined(myo_batch* b, int on) {
-  if (!b) return fail(MYO_ERR_ARG, "null batch");
-  b->pipelined = on != 0;
-  return MYO_OK;
-}
-int myo_outputs_join(myo_batch* b, void* stream) {
-  if (!b) return fail(MYO_ERR_ARG, "null batch");
-  return joinOutputs(b, stream);
-}
+// Round 1 had a separate wide-output kernel that could be pipelined under the next step.  Every field is now written by
+// the phase that produces it, so there is nothing to pipeline or join: both calls are accepted and do nothing.
+int myo_batch_set_pipelined(myo_batch* b, int on) { (void)on; return b ? MYO_OK : fail(MYO_ERR_ARG, "null batch"); }
+int myo_outputs_join(myo_batch* b, void* stream) { (void)stream; return b ? MYO_OK : fail(MYO_ERR_ARG, "null batch"); }
 int myo_forward(myo_batch* b, void* stream) { return launch(b, 0, 1, nullptr, 0, stream); }
 int myo_step(myo_batch* b, int nsubsteps, void* stream) {
   if (nsubsteps < 1) return fail(MYO_ERR_ARG, "nsubsteps must be >= 1");
@@ -380,27 +284,26 @@ int myo_step_host(myo_batch* b, int nsubsteps, const float* qpos, const float* q
   if (ctrl && D.nu) ok &= cudaMemcpyAsync(b->F.p[MYO_F_CTRL], ctrl, n * D.nu * 4, cudaMemcpyHostToDevice, s) == cudaSuccess;
   if (!ok) return fail(MYO_ERR_CUDA, "host-to-device copy failed");
   if (nsubsteps < 1) return fail(MYO_ERR_ARG, "nsubsteps must be >= 1");
-  // qpos / qvel / act are final when the step kernel ends: with wide outputs bound, their copies go to a side stream
-  // that waits for the step kernel only and run under the wide-output kernel; the caller's stream joins before returning.
-  bool fork = false;
-  for (int i = 0; i < kNumWideOutFields; i++) fork |= b->F.p[kWideOutFields[i]] != nullptr;
-  if (b->pipelined || !b->mono) fork = false;   // the output kernel itself leaves the caller's stream: the copies follow the step kernel there
-  if (fork && (rc = ensureSide(b)) != MYO_OK) return rc;
-  rc = launch(b, nsubsteps, 0, nullptr, 0, stream, fork ? (cudaEvent_t)b->ev_step : nullptr);
+  rc = launch(b, nsubsteps, 0, nullptr, 0, stream);
   if (rc) return rc;
-  cudaStream_t cs = fork ? (cudaStream_t)b->copy_stream : s;
-  if (fork) ok &= cudaStreamWaitEvent(cs, (cudaEvent_t)b->ev_step, 0) == cudaSuccess;
-  if (qpos_out) ok &= cudaMemcpyAsync(qpos_out, b->F.p[MYO_F_QPOS], n * D.nq * 4, cudaMemcpyDeviceToHost, cs) == cudaSuccess;
-  if (qvel_out) ok &= cudaMemcpyAsync(qvel_out, b->F.p[MYO_F_QVEL], n * D.nv * 4, cudaMemcpyDeviceToHost, cs) == cudaSuccess;
-  if (act_out && D.na) ok &= cudaMemcpyAsync(act_out, b->F.p[MYO_F_ACT], n * D.na * 4, cudaMemcpyDeviceToHost, cs) == cudaSuccess;
-  if (fork) {
-    ok &= cudaEventRecord((cudaEvent_t)b->ev_copy, cs) == cudaSuccess;
-    ok &= cudaStreamWaitEvent(s, (cudaEvent_t)b->ev_copy, 0) == cudaSuccess;
-  }
+  if (qpos_out) ok &= cudaMemcpyAsync(qpos_out, b->F.p[MYO_F_QPOS], n * D.nq * 4, cudaMemcpyDeviceToHost, s) == cudaSuccess;
+  if (qvel_out) ok &= cudaMemcpyAsync(qvel_out, b->F.p[MYO_F_QVEL], n * D.nv * 4, cudaMemcpyDeviceToHost, s) == cudaSuccess;
+  if (act_out && D.na) ok &= cudaMemcpyAsync(act_out, b->F.p[MYO_F_ACT], n * D.na * 4, cudaMemcpyDeviceToHost, s) == cudaSuccess;
   if (!ok || cudaStreamSynchronize(s) != cudaSuccess) return fail(MYO_ERR_CUDA, std::string("device-to-host copy failed: ") + cudaGetErrorString(cudaGetLastError()));
   return MYO_OK;
 }
 
+// developer hooks (not in include/myostep.h): the scratch layout (SmemLayout as ints) and a copy of the scratch to the host
+int myo_debug_layout(const myo_batch* b, int* out, int n) {
+  const int m = (int)(sizeof(SmemLayout) / sizeof(int));
+  for (int i = 0; i < n && i < m; i++) out[i] = ((const int*)&b->L)[i];
+  return m;
+}
+int64_t myo_debug_scratch(myo_batch* b, float* host_out) {
+  const int64_t n = (int64_t)((b->nworld + 31) / 32) * b->L.total * 32;
+  if (host_out && (cudaDeviceSynchronize() != cudaSuccess || cudaMemcpy(host_out, b->scratch, n * sizeof(float), cudaMemcpyDeviceToHost) != cudaSuccess)) return -1;
+  return n;
+}
 int myo_kat_quat(int n, const float* qa, const float* qb, float* prod, float* mat, float* rotated, void* stream) {
   if (n <= 0 || !qa || !qb || !prod || !mat || !rotated) return fail(MYO_ERR_ARG, "bad argument");
   int ndev = 0;

@@ -3,14 +3,13 @@
 // mj_tendon (+mju_wrap), mj_crb / mj_factorM / mj_solveM, mj_fwdVelocity, mj_fwdActuation; plus the collision primitives
 // (closed-form pairs, MPR) and the muscle / impedance curves.
 //
-// The file compiles in two modes from one source:
-//  * TEAM mode (team.cu, -DTEAM=T): T lanes of a warp own one world; items of a loop are striped over the team's lanes,
-//    TSYNC is a __syncwarp over the team.  Used for the data-dependent solver phases (constraint rows, Newton).
-//  * TILE mode (tile.cu, -DTILE=NW): LANE = WORLD.  A CTA of NW warps owns a tile of 32 consecutive worlds; items of a loop
-//    are striped over the WARPS (t.tl = warp index), TSYNC is a CTA barrier.  Every model-table load is warp-uniform and
-//    every access to the scratch or to a [k][nworld] field is one coalesced 128-byte line with all 32 lanes useful.
-// Both run on the same per-world scratch, struct-of-arrays with the WORLD AXIS FASTEST: element k of world w lives at
-// scratch[k * NW + w] (NW = worlds rounded up to 32), the same float offsets (SmemLayout) the host plan computes.
+// LANE = WORLD: a CTA of NW warps owns a tile of 32 consecutive worlds; the items of every loop
+// (frames, sites, tendon units, dofs, rows ...) are striped over the WARPS (t.tl = warp index, TFOR), TSYNC is a CTA
+// barrier.  Every model-table load is warp-uniform and every access to the scratch or to a [k][nworld] field is one
+// coalesced 128-byte line with all 32 lanes useful.
+// Per-world scratch, tile-blocked: scratch[tile][k][32] -- element k of the tile's lane l at tile_base + 32 k + l, the
+// float offsets k (SmemLayout) computed by the host plan.  The element stride is the compile-time constant 32, so the
+// neighbours of an element are immediate offsets of one address register.
 //
 // Replaces (third-party code the reference calls; call sites in include/myostep.h): mj_kinematics, mj_comPos, mj_tendon
 // (+mju_wrap), mj_crb, mj_factorM, mj_transmission, mj_fwdVelocity, mj_fwdActuation, mj_fwdAcceleration.
@@ -27,12 +26,7 @@
 #ifndef GRAD_NOISE
 #define GRAD_NOISE 2e-6f   // float32 noise floor of the Newton gradient relative to the magnitude of its terms
 #endif
-#ifdef TILE
-#define TEAM (t.nw)   // TILE mode: the "team" of a world is the NW warps of its tile's CTA (one lane each); NW = blockDim.x / 32
-#endif
-#ifndef TEAM
-#define TEAM 1   // lanes per world
-#endif
+#define TEAM (t.nw)   // item stride of a loop = the NW warps of the tile's CTA (NW = blockDim.x / 32, a launch parameter)
 struct TParams { DevModel D; SmemLayout L; FieldPtrs F; };
 #define MYO_NSLOT 8
 __constant__ TParams tP[MYO_NSLOT + 1];   // slot MYO_NSLOT stays zero: "materialise nothing" (inner substeps)
@@ -126,34 +120,22 @@ __device__ __noinline__ float pow_(float x, float y) { return powf(x, y); }
 __device__ __noinline__ float cos_(float x) { return cosf(x); }
 __device__ __noinline__ float sin_(float x) { return sinf(x); }
 
-// Per-world scratch: every world owns SmemLayout.total floats, struct-of-arrays over the batch with the world axis
-// fastest (element k of world w at scratch[k * stride + w]).  SP is a strided pointer into one world's column; the
-// products k * stride fit 31 bits (checked when the batch is created).
+// One world's column of the tile-blocked scratch (or of a [n][32] shared-memory block): element i at p[32 i].
+#define SCR 32
 struct SP {
-  float* p; int s;
-  __device__ __forceinline__ float& operator[](int i) const { return p[i * s]; }
-  __device__ __forceinline__ SP operator+(int k) const { SP r; r.p = p + k * s; r.s = s; return r; }
+  float* p;
+  __device__ __forceinline__ float& operator[](int i) const { return p[i * SCR]; }
+  __device__ __forceinline__ SP operator+(int k) const { SP r; r.p = p + k * SCR; return r; }
 };
 struct SPI {
-  int* p; int s;
-  __device__ __forceinline__ int& operator[](int i) const { return p[i * s]; }
+  int* p;
+  __device__ __forceinline__ int& operator[](int i) const { return p[i * SCR]; }
 };
-__device__ __forceinline__ SPI asInt(SP s) { SPI r; r.p = (int*)s.p; r.s = s.s; return r; }
+__device__ __forceinline__ SPI asInt(SP s) { SPI r; r.p = (int*)s.p; return r; }
 
-#ifdef TILE
-// TILE mode: t.tl = warp index inside the CTA; a CTA barrier orders the items of one phase step against the next
+// t.tl = warp index inside the CTA, t.nw = warps of the CTA; a CTA barrier orders the items of one phase step against the next
 struct Tm { int tl, nw; };
 #define TSYNC() __syncthreads()
-#else
-// TEAM mode: a team of TEAM lanes works on one world; 32 / TEAM worlds share a warp.  Teams of one warp may diverge on data
-// (contacts, solver iterations), so every sync / shuffle names only the team's own lanes.
-struct Tm { int tl; unsigned mask; };
-#if TEAM == 1
-#define TSYNC() do { } while (0)
-#else
-#define TSYNC() __syncwarp(t.mask)
-#endif
-#endif
 #ifndef TFOR_UNROLL
 #define TFOR_UNROLL 1
 #endif
@@ -1211,10 +1193,9 @@ __device__ __noinline__ void writeConstraintOutputs(int slot, int fslot, SP sm, 
 }
 
 #define TRI(r) (((r) * ((r) + 1)) >> 1)
-// Sum of a per-item partial over the items of a world.  TEAM mode: butterfly over the team's lanes.  TILE mode: the
-// partials of the NW warps meet in shared memory and every warp adds them in the same (warp) order, so all warps of a
-// tile hold bit-identical totals and take the same branches; must be called in CTA-uniform control flow.
-#ifdef TILE
+// Sum of a per-item partial over the items of a world: the partials of the NW warps meet in shared memory and every warp
+// adds them in the same (warp) order, so all warps of a tile hold bit-identical totals and take the same branches; must
+// be called in CTA-uniform control flow.
 #define MAXW 16   // warps per tile CTA (blockDim <= 512)
 __device__ __noinline__ float tileSum(Tm t, float v) {
   __shared__ float red[MAXW][32];
@@ -1227,14 +1208,6 @@ __device__ __noinline__ float tileSum(Tm t, float v) {
   return s;
 }
 #define TSUM(v) tileSum(t, v)
-#else
-__device__ __forceinline__ float teamSum(Tm t, float v) {
-#pragma unroll
-  for (int o = TEAM / 2; o > 0; o >>= 1) v += __shfl_xor_sync(t.mask, v, o);
-  return v;
-}
-#define TSUM(v) teamSum(t, v)
-#endif
 // ------------------------------------------------------------------------------------------ constraints
 // Rows are never stored densely: a row is (type, id, coef) and its Jacobian is implied -- limit rows are 1-sparse,
 // equality rows 2-sparse, tendon-limit rows reuse the tendon's sparse moment-arm row, contact rows are +- combinations
@@ -1362,23 +1335,6 @@ __device__ __noinline__ void constraintForce(int slot, SP sm, Tm t, int ncon, in
     out[k] = acc + a1;
   }
   TSYNC();
-}
-__device__ __noinline__ void cholSolve(int slot, SP H, SP x, Tm t) {
-  const int nv = tP[slot].D.nv;
-  for (int j = 0; j < nv; j++) {
-    const float xj = x[j] / H[TRI(j) + j];
-    TSYNC();
-    if (t.tl == 0) x[j] = xj;
-    for (int r = j + 1 + t.tl; r < nv; r += TEAM) x[r] = fmaf(-H[TRI(r) + j], xj, x[r]);
-    TSYNC();
-  }
-  for (int j = nv - 1; j >= 0; j--) {
-    const float xj = x[j] / H[TRI(j) + j];
-    TSYNC();
-    if (t.tl == 0) x[j] = xj;
-    for (int r = t.tl; r < j; r += TEAM) x[r] = fmaf(-H[TRI(j) + r], xj, x[r]);
-    TSYNC();
-  }
 }
 // One point of the 1-D cost along the search direction.  `tol` is the convergence threshold for |d0| at this point:
 // MuJoCo's gtol, or the float32 noise floor of the derivative sum when that is larger (the sum cancels to ~eps * mag

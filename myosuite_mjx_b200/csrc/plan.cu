@@ -654,7 +654,8 @@ void myo_make_layout(DevModel& D, int nconmax_req, int njmax_req, SmemLayout& L)
   o = base;
   // overlay B: collision, constraints, solver
   L.cgpose = take(12 * D.ncg); L.con = take(12 * D.nconmax); L.conJ = take(nb * D.nconmax * nv); L.efc = take(10 * D.njmax);
-  L.H = take(nv * nv + nv);   // lower triangle + the factor's diagonal (tile.cu newtonKernel when its block does not fit shared memory) L.nvec = take(6 * nv); L.limrow = take(2 * (D.nlimj + D.nlimt)); L.basev = take(2 * nb * D.nconmax);
+  // H: lower triangle + the factor's diagonal (tile.cu newtonKernel when its block does not fit shared memory)
+  L.H = take(nv * nv + nv); L.nvec = take(6 * nv); L.limrow = take(2 * (D.nlimj + D.nlimt)); L.basev = take(2 * nb * D.nconmax);
   L.cand = take(D.npair);
   L.conU = take(nb * D.nconmax * nv);   // W Jb of the Newton Hessian (tile.cu hessianTile)
   int endB = o;

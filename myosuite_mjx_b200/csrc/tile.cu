@@ -6,11 +6,10 @@
 //  * every access to the per-world scratch and to a [k][nworld] mjData field is one full, coalesced 128-byte line,
 //  * all 32 lanes of every instruction do useful work; lanes differ only on DATA (wrap / no wrap, contact or not),
 //  * a CTA barrier (not a kernel boundary) orders dependent item sets inside a phase; a kernel boundary orders phases.
-// The regular phases are the same source as the TEAM build (common.cuh, compiled here with TILE defined); the collision
-// phase is written for this mode (per-lane candidate lists, ordered compaction by per-warp chunks).
+// The collision phase keeps per-lane candidate lists and compacts in order by per-warp chunks; the constraint solve runs the
+// tile's 32 worlds in lock step (per-lane activity masks).
 //
-// One mj_step = kin -> tendon -> inertia -> collide -> velact -> [team.cu solveKernel] -> finish   (api.cu).
-#define TILE 1   // common.cuh: TEAM = t.nw, the warps per tile -- a launch parameter (blockDim.x / 32), not a build constant
+// One mj_step = kin -> tendon -> inertia -> collide -> velact -> newton -> conout -> finish   (api.cu).
 #include "common.cuh"
 
 namespace {
@@ -20,22 +19,22 @@ enum { FIN_EULER = 1, FIN_STATE = 2, FIN_WARM = 4, FIN_ACC = 8 };
 enum { WS_STATUS = 0, WS_TIME = 1, WS_SKIP = 2 };
 
 struct Ctx { SP sm; Tm t; World W; bool live; };
-__device__ __forceinline__ Ctx tileCtx(int nworld, int stride, const int* mask, float* scratch) {
+__device__ __forceinline__ Ctx tileCtx(int slot, int nworld, const int* mask, float* scratch) {
   Ctx c;
   const int lane = threadIdx.x & 31;
   c.t.tl = threadIdx.x >> 5; c.t.nw = blockDim.x >> 5;
   const size_t w = (size_t)blockIdx.x * 32 + lane;
   c.live = w < (size_t)nworld && !(mask && !mask[w]);
   c.W.w = w; c.W.nw = (size_t)nworld;
-  c.sm.p = scratch + w; c.sm.s = stride;
+  c.sm.p = scratch + (size_t)blockIdx.x * tP[slot].L.total * SCR + lane;   // this tile's block, this lane's column
   return c;
 }
 
 // ------------------------------------------------------------------------------------------ kin: state in, mj_kinematics, mj_comPos
-__global__ void __launch_bounds__(512) kinKernel(int slot, int fslot, int nworld, int stride, const int* __restrict__ mask, int flags,
+__global__ void __launch_bounds__(512) kinKernel(int slot, int fslot, int nworld, const int* __restrict__ mask, int flags,
                                                  float* __restrict__ scratch) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L; const FieldPtrs& F = tP[slot].F;
-  Ctx c = tileCtx(nworld, stride, mask, scratch);
+  Ctx c = tileCtx(slot, nworld, mask, scratch);
   if (!c.live) return;   // exited lanes are not waited for by the CTA barriers below
   SP sm = c.sm; Tm t = c.t; World W = c.W;
   __shared__ int sBad[32];
@@ -80,17 +79,17 @@ __global__ void __launch_bounds__(512) kinKernel(int slot, int fslot, int nworld
 }
 
 // ------------------------------------------------------------------------------------------ tendon: mj_tendon (+ path points)
-__global__ void __launch_bounds__(512) tendonKernel(int slot, int fslot, int nworld, int stride, const int* __restrict__ mask, float* __restrict__ scratch) {
-  Ctx c = tileCtx(nworld, stride, mask, scratch);
+__global__ void __launch_bounds__(512) tendonKernel(int slot, int fslot, int nworld, const int* __restrict__ mask, float* __restrict__ scratch) {
+  Ctx c = tileCtx(slot, nworld, mask, scratch);
   if (!c.live) return;
   tendons(slot, fslot, c.sm, c.t, c.W);
 }
 
 // ------------------------------------------------------------------------------------------ inertia: mj_crb, mj_factorM (+ Euler's M + h B factor)
-__global__ void __launch_bounds__(512) inertiaKernel(int slot, int fslot, int nworld, int stride, const int* __restrict__ mask, int euler,
+__global__ void __launch_bounds__(512) inertiaKernel(int slot, int fslot, int nworld, const int* __restrict__ mask, int euler,
                                                      float* __restrict__ scratch) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
-  Ctx c = tileCtx(nworld, stride, mask, scratch);
+  Ctx c = tileCtx(slot, nworld, mask, scratch);
   if (!c.live) return;
   SP sm = c.sm; Tm t = c.t;
   inertia(slot, fslot, sm, t, c.W);
@@ -104,10 +103,10 @@ __global__ void __launch_bounds__(512) inertiaKernel(int slot, int fslot, int nw
 }
 
 // ------------------------------------------------------------------------------------------ velact: mj_fwdVelocity, mj_fwdActuation, mj_fwdAcceleration
-__global__ void __launch_bounds__(512) velactKernel(int slot, int fslot, int nworld, int stride, const int* __restrict__ mask, int posvel,
+__global__ void __launch_bounds__(512) velactKernel(int slot, int fslot, int nworld, const int* __restrict__ mask, int posvel,
                                                     float* __restrict__ scratch) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
-  Ctx c = tileCtx(nworld, stride, mask, scratch);
+  Ctx c = tileCtx(slot, nworld, mask, scratch);
   if (!c.live) return;
   SP sm = c.sm; Tm t = c.t; World W = c.W;
   velocity(slot, fslot, sm, t, W);
@@ -148,9 +147,9 @@ __device__ __forceinline__ bool broadPass(const DevModel& D, const SmemLayout& L
 }
 __device__ __forceinline__ int warpMax(int v) { return __reduce_max_sync(__activemask(), v); }
 
-__global__ void __launch_bounds__(512) collideKernel(int slot, int nworld, int stride, const int* __restrict__ mask, float* __restrict__ scratch) {
+__global__ void __launch_bounds__(512) collideKernel(int slot, int nworld, const int* __restrict__ mask, float* __restrict__ scratch) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
-  Ctx c = tileCtx(nworld, stride, mask, scratch);
+  Ctx c = tileCtx(slot, nworld, mask, scratch);
   if (!c.live) return;
   SP sm = c.sm; Tm t = c.t;
   const int lane = threadIdx.x & 31, nw = t.nw;
@@ -732,14 +731,14 @@ __device__ __noinline__ int newtonTile(int slot, SP sm, Tm t, const NewtonMem& M
 // Shared memory of a tile: Hessian (lower triangle), its factor's diagonal and six nv-vectors, [element][32 lanes].  When a
 // model's block does not fit (nv beyond ~55), the same kernel runs with everything in the world's scratch column.
 static inline size_t newtonSmemFloats(int nv) { return (size_t)(TRI(nv) + 7 * nv) * 32; }
-#define NEWTON_SMEM_MAX (200 * 1024)
-__global__ void __launch_bounds__(512) newtonKernel(int slot, int fslot, int nworld, int stride, const int* __restrict__ mask, int check_acc,
+#define NEWTON_SMEM_MAX (190 * 1024)   // + ~31 KB of static reduction / scan buffers <= 227 KB per CTA
+__global__ void __launch_bounds__(512) newtonKernel(int slot, int fslot, int nworld, const int* __restrict__ mask, int check_acc,
                                                     int use_smem, float* __restrict__ scratch) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
   extern __shared__ float tileShared[];
   __shared__ int sBad[32];
   const int lane = threadIdx.x & 31;
-  Ctx c = tileCtx(nworld, stride, mask, scratch);
+  Ctx c = tileCtx(slot, nworld, mask, scratch);
   const unsigned lmask = __ballot_sync(0xffffffffu, c.live);
   if (!c.live) return;
   SP sm = c.sm; Tm t = c.t;
@@ -757,7 +756,7 @@ __global__ void __launch_bounds__(512) newtonKernel(int slot, int fslot, int nwo
     NewtonMem M;
     if (use_smem) {
       float* p = tileShared + lane;
-      auto take = [&](int n) { SP r; r.p = p; r.s = 32; p += n * 32; return r; };
+      auto take = [&](int n) { SP r; r.p = p; p += n * SCR; return r; };
       M.H = take(TRI(nv)); M.Hd = take(nv); M.qacc = take(nv); M.Ma = take(nv); M.grad = take(nv); M.search = take(nv); M.Mv = take(nv); M.tmp = take(nv);
     } else {
       M.H = sm + L.H; M.Hd = sm + L.H + TRI(nv); M.qacc = sm + L.nvec; M.Ma = M.qacc + nv; M.grad = M.Ma + nv; M.search = M.grad + nv;
@@ -793,10 +792,10 @@ __global__ void __launch_bounds__(512) newtonKernel(int slot, int fslot, int nwo
 // ------------------------------------------------------------------------------------------ finish: mj_Euler, state out
 // mj_Euler with implicit joint damping (the factor of M + h B comes from inertiaKernel), quaternion integration on the
 // manifold; then the state and the per-dof results of the solve go out as full lines.
-__global__ void __launch_bounds__(512) finishKernel(int slot, int fslot, int nworld, int stride, const int* __restrict__ mask, int flags,
+__global__ void __launch_bounds__(512) finishKernel(int slot, int fslot, int nworld, const int* __restrict__ mask, int flags,
                                                     float* __restrict__ scratch) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L; const FieldPtrs& F = tP[slot].F;
-  Ctx c = tileCtx(nworld, stride, mask, scratch);
+  Ctx c = tileCtx(slot, nworld, mask, scratch);
   if (!c.live) return;
   SP sm = c.sm; Tm t = c.t; World W = c.W;
   const int nq = D.nq, nv = D.nv, na = D.na, nu = D.nu;
@@ -865,9 +864,9 @@ __global__ void __launch_bounds__(512) finishKernel(int slot, int fslot, int nwo
 // ------------------------------------------------------------------------------------------ conout: contact / constraint records
 // contact_* and efc_* (padded to nconmax / njmax, efc_J expanded to dense rows): pure stores, no ordering between items, so
 // the items are striped over the warps of gridDim.y CTAs per tile.
-__global__ void __launch_bounds__(256) conoutKernel(int slot, int fslot, int nworld, int stride, const int* __restrict__ mask, float* __restrict__ scratch) {
+__global__ void __launch_bounds__(256) conoutKernel(int slot, int fslot, int nworld, const int* __restrict__ mask, float* __restrict__ scratch) {
   const SmemLayout& L = tP[slot].L;
-  Ctx c = tileCtx(nworld, stride, mask, scratch);
+  Ctx c = tileCtx(slot, nworld, mask, scratch);
   if (!c.live) return;
   Tm t; t.nw = c.t.nw * gridDim.y; t.tl = blockIdx.y * c.t.nw + c.t.tl;
   SP sm = c.sm;
@@ -900,36 +899,36 @@ int myo_tile_upload(int slot, const DevModel& D, const SmemLayout& L, const Fiel
 static int envInt(const char* name, int dflt) { const char* e = getenv(name); return e ? atoi(e) : dflt; }
 // Warps per tile of each kernel (developer knobs MYO_NW_*): enough warps per SM to hide the scratch latency, few enough
 // that the item loops still have work for every warp.
-int myo_tile_launch(int kernel, int slot, int fslot, int nworld, int stride, const int* mask, int flags, float* scratch, void* stream) {
+int myo_tile_launch(int kernel, int slot, int fslot, int nworld, const int* mask, int flags, float* scratch, void* stream) {
   static const int nwKin = envInt("MYO_NW_KIN", 16), nwTen = envInt("MYO_NW_TEN", 16), nwIne = envInt("MYO_NW_INE", 8),
                    nwCol = envInt("MYO_NW_COL", 16), nwVel = envInt("MYO_NW_VEL", 8), nwFin = envInt("MYO_NW_FIN", 8),
                    nwOut = envInt("MYO_NW_OUT", 8), yOut = envInt("MYO_Y_OUT", 4), nwNew = envInt("MYO_NW_NEWTON", 8);
   const int tiles = (nworld + 31) / 32;
   cudaStream_t st = (cudaStream_t)stream;
   switch (kernel) {
-    case MYO_K_KIN: kinKernel<<<tiles, 32 * nwKin, 0, st>>>(slot, fslot, nworld, stride, mask, flags, scratch); break;
-    case MYO_K_TENDON: tendonKernel<<<tiles, 32 * nwTen, 0, st>>>(slot, fslot, nworld, stride, mask, scratch); break;
-    case MYO_K_INERTIA: inertiaKernel<<<tiles, 32 * nwIne, 0, st>>>(slot, fslot, nworld, stride, mask, flags, scratch); break;
-    case MYO_K_COLLIDE: collideKernel<<<tiles, 32 * nwCol, 0, st>>>(slot, nworld, stride, mask, scratch); break;
-    case MYO_K_VELACT: velactKernel<<<tiles, 32 * nwVel, 0, st>>>(slot, fslot, nworld, stride, mask, flags, scratch); break;
-    case MYO_K_FINISH: finishKernel<<<tiles, 32 * nwFin, 0, st>>>(slot, fslot, nworld, stride, mask, flags, scratch); break;
+    case MYO_K_KIN: kinKernel<<<tiles, 32 * nwKin, 0, st>>>(slot, fslot, nworld, mask, flags, scratch); break;
+    case MYO_K_TENDON: tendonKernel<<<tiles, 32 * nwTen, 0, st>>>(slot, fslot, nworld, mask, scratch); break;
+    case MYO_K_INERTIA: inertiaKernel<<<tiles, 32 * nwIne, 0, st>>>(slot, fslot, nworld, mask, flags, scratch); break;
+    case MYO_K_COLLIDE: collideKernel<<<tiles, 32 * nwCol, 0, st>>>(slot, nworld, mask, scratch); break;
+    case MYO_K_VELACT: velactKernel<<<tiles, 32 * nwVel, 0, st>>>(slot, fslot, nworld, mask, flags, scratch); break;
+    case MYO_K_FINISH: finishKernel<<<tiles, 32 * nwFin, 0, st>>>(slot, fslot, nworld, mask, flags, scratch); break;
     case MYO_K_NEWTON: {
       const int nv = flags >> 8;   // the host passes nv in the upper bits (the model lives in constant memory)
       size_t shmem = newtonSmemFloats(nv) * sizeof(float);
       const int use_smem = shmem <= NEWTON_SMEM_MAX ? 1 : 0;
       if (!use_smem) shmem = 0;
-      static bool configured[64] = {false};
+      static size_t configured[64] = {0};   // per device: largest dynamic shared-memory size opted in to so far
       int dev = 0;
       if (shmem > 48 * 1024) {
         if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return -1;
-        if (!configured[dev]) {
-          if (cudaFuncSetAttribute(newtonKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, NEWTON_SMEM_MAX) != cudaSuccess) return -1;
-          configured[dev] = true;
+        if (configured[dev] < shmem) {
+          if (cudaFuncSetAttribute(newtonKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shmem) != cudaSuccess) return -1;
+          configured[dev] = shmem;
         }
       }
-      newtonKernel<<<tiles, 32 * nwNew, shmem, st>>>(slot, fslot, nworld, stride, mask, flags & 1, use_smem, scratch);
+      newtonKernel<<<tiles, 32 * nwNew, shmem, st>>>(slot, fslot, nworld, mask, flags & 1, use_smem, scratch);
     } break;
-    case MYO_K_CONOUT: conoutKernel<<<dim3(tiles, yOut), 32 * nwOut, 0, st>>>(slot, fslot, nworld, stride, mask, scratch); break;
+    case MYO_K_CONOUT: conoutKernel<<<dim3(tiles, yOut), 32 * nwOut, 0, st>>>(slot, fslot, nworld, mask, scratch); break;
     default: return -1;
   }
   return cudaPeekAtLastError() == cudaSuccess ? 0 : -1;

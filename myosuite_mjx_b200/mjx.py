@@ -159,7 +159,6 @@ class Data:
         h = ctypes.c_void_p()
         _lib.check(L.myo_batch_create(self.model._h, self.nworld, self.nconmax, self.njmax, ctypes.byref(h)))
         d._h, d.nconmax, d.njmax, d._t = h, self.nconmax, self.njmax, {}
-        self.join()
         d.smem_bytes, d.team, d.ctas_per_sm = self.smem_bytes, L.myo_batch_team(h), 1
         d.engine = "phase" if L.myo_batch_engine(h) == 1 else "mono"
         if self.__dict__.get("_pipelined"):
