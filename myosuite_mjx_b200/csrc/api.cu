@@ -156,6 +156,8 @@ void myo_batch_destroy(myo_batch* b) {
   if (!b) return;
   cudaSetDevice(b->model->device);
   for (void* p : b->owned) cudaFree(p);
+  for (int i = 0; i < 2; i++) if (b->side[i]) { cudaStreamSynchronize((cudaStream_t)b->side[i]); cudaStreamDestroy((cudaStream_t)b->side[i]); }
+  for (int i = 0; i < 6; i++) if (b->ev[i]) cudaEventDestroy((cudaEvent_t)b->ev[i]);
   if (b->slot >= 0) g_slot_used[b->slot] = false;
   delete b;
 }
@@ -213,16 +215,22 @@ static int launchPhases(myo_batch* b, int nsub, int forward_only, const int32_t*
     if ((rc = clearPathPoints(b, stream)) != MYO_OK) return rc;
     b->dirty = false;
   }
+  static const bool concurrent = !(getenv("MYO_CONCURRENT") && atoi(getenv("MYO_CONCURRENT")) == 0);   // developer knob
+  if (concurrent && !b->side[0]) {
+    for (int i = 0; i < 2; i++) { cudaStream_t cs; if (cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking) != cudaSuccess) return fail(MYO_ERR_CUDA, "side stream creation failed"); b->side[i] = cs; }
+    for (int i = 0; i < 6; i++) { cudaEvent_t e; if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess) return fail(MYO_ERR_CUDA, "event creation failed"); b->ev[i] = e; }
+  }
   const bool posvel = forward_only == 2;
   const int nloop = forward_only ? 1 : nsub;
   const int slot = b->slot, nw = b->nworld;
   float* scr = b->scratch;
   static const bool debug_sync = getenv("MYO_DEBUG_SYNC") != nullptr;   // developer knob: synchronise after every kernel and name the one that failed
+  void* cur = stream;   // the stream the next kernel goes to
   auto tile = [&](int k, int fslot, int flags) {
     g_launches++;
-    int r = myo_tile_launch(k, slot, fslot, nw, mask, flags, scr, stream);
+    int r = myo_tile_launch(k, slot, fslot, nw, mask, flags, scr, cur);
     if (debug_sync && r == 0) {
-      const cudaError_t e = cudaStreamSynchronize((cudaStream_t)stream);
+      const cudaError_t e = cudaStreamSynchronize((cudaStream_t)cur);
       if (e != cudaSuccess) { fprintf(stderr, "[myostep] tile kernel %d failed: %s\n", k, cudaGetErrorString(e)); r = -1; }
     }
     return r;
@@ -235,18 +243,37 @@ static int launchPhases(myo_batch* b, int nsub, int forward_only, const int32_t*
     const bool first = sub == 0, last = sub == nloop - 1;
     const int fslot = last ? slot : MYO_PARAM_SLOTS;   // slot MYO_PARAM_SLOTS: no field bound, "materialise nothing"
     ok &= tile(MYO_K_KIN, fslot, (first ? (do_reset ? MYO_KIN_RESET : MYO_KIN_LOAD) : 0) | (forward_only ? 0 : MYO_KIN_CHECK)) == 0; STOP_HERE();
-    ok &= tile(MYO_K_TENDON, fslot, 0) == 0; STOP_HERE();
-    if (!posvel) {
-      ok &= tile(MYO_K_INERTIA, fslot, forward_only ? 0 : 1) == 0; STOP_HERE();
-      ok &= tile(MYO_K_COLLIDE, fslot, 0) == 0; STOP_HERE();
+    if (concurrent && !posvel && debug_stop < 0) {
+      // fork: tendon and inertia on the side streams, collide on the caller's; join before velact
+      auto S = [&](int i) { return (cudaStream_t)b->side[i]; };
+      auto E = [&](int i) { return (cudaEvent_t)b->ev[i]; };
+      ok &= cudaEventRecord(E(0), (cudaStream_t)stream) == cudaSuccess;
+      ok &= cudaStreamWaitEvent(S(0), E(0), 0) == cudaSuccess && cudaStreamWaitEvent(S(1), E(0), 0) == cudaSuccess;
+      cur = b->side[0]; ok &= tile(MYO_K_TENDON, fslot, 0) == 0;
+      cur = b->side[1]; ok &= tile(MYO_K_INERTIA, fslot, forward_only ? 0 : 1) == 0;
+      cur = stream;     ok &= tile(MYO_K_COLLIDE, fslot, 0) == 0;
+      ok &= cudaEventRecord(E(1), S(0)) == cudaSuccess && cudaEventRecord(E(2), S(1)) == cudaSuccess;
+      ok &= cudaStreamWaitEvent((cudaStream_t)stream, E(1), 0) == cudaSuccess && cudaStreamWaitEvent((cudaStream_t)stream, E(2), 0) == cudaSuccess;
+    } else {
+      ok &= tile(MYO_K_TENDON, fslot, 0) == 0; STOP_HERE();
+      if (!posvel) {
+        ok &= tile(MYO_K_INERTIA, fslot, forward_only ? 0 : 1) == 0; STOP_HERE();
+        ok &= tile(MYO_K_COLLIDE, fslot, 0) == 0; STOP_HERE();
+      }
     }
     ok &= tile(MYO_K_VELACT, fslot, posvel ? 1 : 0) == 0; STOP_HERE();
     if (posvel) break;
     ok &= tile(MYO_K_NEWTON, fslot, (forward_only ? 0 : 1) | (b->D.nv << 8)) == 0;
     STOP_HERE();
-    if (last && b->conout) { ok &= tile(MYO_K_CONOUT, fslot, 0) == 0; STOP_HERE(); }
+    const bool forkout = concurrent && last && b->conout && debug_stop < 0;
+    if (forkout) {   // the contact / constraint records go out on a side stream under mj_Euler and the state outputs
+      ok &= cudaEventRecord((cudaEvent_t)b->ev[3], (cudaStream_t)stream) == cudaSuccess && cudaStreamWaitEvent((cudaStream_t)b->side[0], (cudaEvent_t)b->ev[3], 0) == cudaSuccess;
+      cur = b->side[0]; ok &= tile(MYO_K_CONOUT, fslot, 0) == 0; cur = stream;
+      ok &= cudaEventRecord((cudaEvent_t)b->ev[4], (cudaStream_t)b->side[0]) == cudaSuccess;
+    } else if (last && b->conout) { ok &= tile(MYO_K_CONOUT, fslot, 0) == 0; STOP_HERE(); }
     ok &= tile(MYO_K_FINISH, fslot, (forward_only ? 0 : MYO_FIN_EULER) | (last && (!forward_only || do_reset) ? MYO_FIN_STATE : 0) |
                                         (last ? MYO_FIN_WARM | MYO_FIN_ACC : 0)) == 0;
+    if (forkout) ok &= cudaStreamWaitEvent((cudaStream_t)stream, (cudaEvent_t)b->ev[4], 0) == cudaSuccess;
   }
   if (!ok) return fail(MYO_ERR_CUDA, std::string("kernel launch failed: ") + cudaGetErrorString(cudaGetLastError()));
   return MYO_OK;

@@ -35,6 +35,10 @@ struct myo_batch {
   bool conout;   // some contact / constraint record field is bound: conoutKernel runs
   void* wrap_cleared[2] = {nullptr, nullptr};   // wrap_obj / wrap_xpos buffers already zeroed once (api.cu)
   float* scratch; // per-world intermediates, tile-blocked: [tiles][L.total][32]
+  // the phases that depend only on the kinematics (tendon, inertia, collide) and the two tails of a step (conout, finish) run
+  // concurrently: two library-owned side streams fork from and join the caller's stream with events (graph-capturable)
+  void* side[2] = {nullptr, nullptr};
+  void* ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
   std::vector<void*> owned;
 };
 

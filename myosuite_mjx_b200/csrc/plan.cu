@@ -651,13 +651,14 @@ void myo_make_layout(DevModel& D, int nconmax_req, int njmax_req, SmemLayout& L)
   o = base;
   L.tmpbody = take(13 * D.nbody);   // position-output stage only (before the tendon stage)
   endA = std::max(endA, o);
-  o = base;
-  // overlay B: collision, constraints, solver
+  o = endA;   // no overlay: the tendon, inertia and collision phases of a step run concurrently on separate streams (api.cu)
+  // region B: collision, constraints, solver
   L.cgpose = take(12 * D.ncg); L.con = take(12 * D.nconmax); L.conJ = take(nb * D.nconmax * nv); L.efc = take(10 * D.njmax);
   // H: lower triangle + the factor's diagonal (tile.cu newtonKernel when its block does not fit shared memory)
   L.H = take(nv * nv + nv); L.nvec = take(6 * nv); L.limrow = take(2 * (D.nlimj + D.nlimt)); L.basev = take(2 * nb * D.nconmax);
   L.cand = take(D.npair);
   L.conU = take(nb * D.nconmax * nv);   // W Jb of the Newton Hessian (tile.cu hessianTile)
+  L.conW = take(8 * D.nconmax);         // per-contact weights of the active pyramid rows in base-row space
   int endB = o;
   L.total = std::max(endA, endB);
   L.nv = nv; L.hshared = 0;

@@ -374,24 +374,32 @@ __device__ __noinline__ int makeConstraintTile(int slot, SP sm, Tm t, int ncon, 
     if (unfit < nefc) { *status |= MYO_WORLD_NEFC_OVERFLOW; nefc = min(unfit, njmax); }
     // base Jacobian rows: one item = (contact, dof); contacts past the lane's own count up to the tile's get zero rows
     // (the Hessian product below runs over the tile's count)
-    for (int idx = t.tl; idx < nconT * nv; idx += nw) {
-      const int c = idx / nv, k = idx - c * nv;
+    for (int c = t.tl; c < nconT; c += nw) {
       auto cr = sm + L.con + 12 * c;
-      auto J = sm + L.conJ + (c * nb) * nv + k;
-      if (c >= ncon || !(((unsigned)__float_as_int(cr[10 + (k >> 5)]) >> (k & 31)) & 1u)) {   // dof k moves both bodies or neither
-        J[0] = 0.f; if (nb > 1) { J[nv] = 0.f; J[2 * nv] = 0.f; } if (nb > 3) J[3 * nv] = 0.f; continue;
+      auto Jc = sm + L.conJ + (c * nb) * nv;
+      if (c >= ncon) {
+        for (int k = 0; k < nb * nv; k++) Jc[k] = 0.f;
+        continue;
       }
+      const unsigned mlo = (unsigned)__float_as_int(cr[10]), mhi = (unsigned)__float_as_int(cr[11]);
       const int f1 = D.cg_frame[D.pair_cg1[__float_as_int(cr[7])]];
-      const int in1 = (D.fr_mask[2 * f1 + (k >> 5)] >> (k & 31)) & 1;   // it moves exactly one of them: the first (-) or the second (+)
+      const unsigned f1lo = (unsigned)D.fr_mask[2 * f1], f1hi = (unsigned)D.fr_mask[2 * f1 + 1];
       const f3 pos = ld3(cr + 1), n = ld3(cr + 4);
       f3 y, z; makeFrame(n, &y, &z);
-      const float sgn = in1 ? -1.f : 1.f;
-      auto cd = sm + L.cdof + 6 * k;
-      const f3 jr = ld3(cd) * sgn;
-      const f3 jp = (ld3(cd + 3) + cross(ld3(cd), pos - ld3(sm + L.rootcom + 3 * D.fr_root[D.dof_frame[k]]))) * sgn;
-      J[0] = dot(n, jp);
-      if (nb > 1) { J[nv] = dot(y, jp); J[2 * nv] = dot(z, jp); }
-      if (nb > 3) J[3 * nv] = dot(n, jr);
+      for (int k = 0; k < nv; k++) {
+        auto J = Jc + k;
+        const unsigned bit = 1u << (k & 31);
+        if (!((k < 32 ? mlo : mhi) & bit)) {   // dof k moves both bodies or neither
+          J[0] = 0.f; if (nb > 1) { J[nv] = 0.f; J[2 * nv] = 0.f; } if (nb > 3) J[3 * nv] = 0.f; continue;
+        }
+        const float sgn = ((k < 32 ? f1lo : f1hi) & bit) ? -1.f : 1.f;   // it moves exactly one of them: the first (-) or the second (+)
+        auto cd = sm + L.cdof + 6 * k;
+        const f3 jr = ld3(cd) * sgn;
+        const f3 jp = (ld3(cd + 3) + cross(ld3(cd), pos - ld3(sm + L.rootcom + 3 * D.fr_root[D.dof_frame[k]]))) * sgn;
+        J[0] = dot(n, jp);
+        if (nb > 1) { J[nv] = dot(y, jp); J[2 * nv] = dot(z, jp); }
+        if (nb > 3) J[3 * nv] = dot(n, jr);
+      }
     }
     TSYNC();
     auto bx = sm + L.basev;
@@ -469,16 +477,13 @@ __device__ __noinline__ void hessianTile(int slot, SP sm, Tm t, SP H, SP Hd, int
     }
   TSYNC();
   if (nconT > 0) {   // tile-uniform
-    // weights in base-row space: W = sum_p D_p w_p w_p^T, w_p = e_n +- mu e_t; then U = W Jb per (contact, dof)
-    auto U = sm + L.conU;
-    for (int idx = t.tl; idx < nconT * nv; idx += nw) {
-      const int c = idx / nv, k = idx - c * nv;
+    // weights in base-row space, once per contact: W = sum_p D_p w_p w_p^T, w_p = e_n +- mu e_t  ->  conW[8 c] = Wnn, Wnt[3], Wtt[3]
+    // (the row records sit at per-lane addresses: these are the only uncoalesced loads of the assembly)
+    for (int c = t.tl; c < nconT; c += nw) {
       auto cr = sm + L.con + 12 * c;
       float Wnn = 0.f, Wnt[3] = {0.f, 0.f, 0.f}, Wtt[3] = {0.f, 0.f, 0.f};
-      int dim = 1;
       if (c < ncon) {
-        const int adr = __float_as_int(cr[8]);
-        dim = __float_as_int(cr[9]);
+        const int adr = __float_as_int(cr[8]), dim = __float_as_int(cr[9]);
         if (adr >= 0) {
           if (dim == 1) { if (EFC(E_JAR, adr) < 0.f) Wnn = EFC(E_D, adr); }
           else
@@ -490,15 +495,29 @@ __device__ __noinline__ void hessianTile(int slot, SP sm, Tm t, SP H, SP Hd, int
             }
         }
       }
-      auto J = sm + L.conJ + (c * nb) * nv + k; auto Uo = U + (c * nb) * nv + k;
-      const float jn = J[0];
-      float un = Wnn * jn;
-      for (int q = 1; q < nb; q++) {
-        const float jt = J[q * nv];
-        un = fmaf(Wnt[q - 1], jt, un);
-        Uo[q * nv] = fmaf(Wnt[q - 1], jn, Wtt[q - 1] * jt);
+      auto Wo = sm + L.conW + 8 * c;
+      Wo[0] = Wnn; Wo[1] = Wnt[0]; Wo[2] = Wnt[1]; Wo[3] = Wnt[2]; Wo[4] = Wtt[0]; Wo[5] = Wtt[1]; Wo[6] = Wtt[2];
+    }
+    TSYNC();
+    // U = W Jb: a warp takes whole contacts and walks their dofs
+    for (int c = t.tl; c < nconT; c += nw) {
+      auto Wi = sm + L.conW + 8 * c;
+      const float Wnn = Wi[0], Wnt0 = Wi[1], Wnt1 = Wi[2], Wnt2 = Wi[3], Wtt0 = Wi[4], Wtt1 = Wi[5], Wtt2 = Wi[6];
+      auto J = sm + L.conJ + (c * nb) * nv; auto Uo = sm + L.conU + (c * nb) * nv;
+      if (nb == 3) {
+        for (int k = 0; k < nv; k++) {
+          const float jn = J[k], j1 = J[nv + k], j2 = J[2 * nv + k];
+          Uo[k] = fmaf(Wnt1, j2, fmaf(Wnt0, j1, Wnn * jn)); Uo[nv + k] = fmaf(Wnt0, jn, Wtt0 * j1); Uo[2 * nv + k] = fmaf(Wnt1, jn, Wtt1 * j2);
+        }
+      } else if (nb == 4) {
+        for (int k = 0; k < nv; k++) {
+          const float jn = J[k], j1 = J[nv + k], j2 = J[2 * nv + k], j3 = J[3 * nv + k];
+          Uo[k] = fmaf(Wnt2, j3, fmaf(Wnt1, j2, fmaf(Wnt0, j1, Wnn * jn)));
+          Uo[nv + k] = fmaf(Wnt0, jn, Wtt0 * j1); Uo[2 * nv + k] = fmaf(Wnt1, jn, Wtt1 * j2); Uo[3 * nv + k] = fmaf(Wnt2, jn, Wtt2 * j3);
+        }
+      } else {
+        for (int k = 0; k < nv; k++) Uo[k] = Wnn * J[k];
       }
-      Uo[0] = un;
     }
     TSYNC();
     const int nblk = (nv + 3) >> 2, nB = (nblk * (nblk + 1)) >> 1, nbase = nb * nconT;
