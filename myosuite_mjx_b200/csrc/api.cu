@@ -141,6 +141,11 @@ int myo_batch_create(const myo_model* m, int nworld, int nconmax, int njmax, myo
     const size_t bytes = (size_t)((nworld + 31) / 32) * b->L.total * 32 * sizeof(float);
     if (cudaMalloc(&p, bytes) != cudaSuccess || cudaMemset(p, 0, bytes) != cudaSuccess) { g_slot_used[b->slot] = false; delete b; return fail(MYO_ERR_CUDA, "cudaMalloc of the per-world scratch failed"); }
     b->owned.push_back(p); b->scratch = (float*)p;
+    // work list of the convex narrow phase: at most every MPR-type candidate pair of every world
+    b->X.mpr_cap = (int)std::min<int64_t>((int64_t)nworld * std::max(1, b->D.nmprpair), (int64_t)1 << 30);
+    void* q = nullptr;
+    if (cudaMalloc(&q, (size_t)b->X.mpr_cap * sizeof(int2) + 256) != cudaSuccess || cudaMemset(q, 0, 256) != cudaSuccess) { myo_batch_destroy(b); return fail(MYO_ERR_CUDA, "cudaMalloc of the narrow-phase work list failed"); }
+    b->owned.push_back(q); b->X.mpr_count = (int*)q; b->X.mpr_list = (int2*)((char*)q + 256);
   }
   // library-owned default state buffers (bind overrides them)
   for (int f : kStateFields) {
@@ -205,7 +210,7 @@ static int clearPathPoints(myo_batch* b, void* stream) {
 static int launchPhases(myo_batch* b, int nsub, int forward_only, const int32_t* mask, int do_reset, void* stream) {
   int rc;
   if (b->dirty) {
-    if (myo_tile_upload(b->slot, b->D, b->L, b->F, stream) != 0) return fail(MYO_ERR_CUDA, "parameter upload failed");
+    if (myo_tile_upload(b->slot, b->D, b->L, b->F, b->X, stream) != 0) return fail(MYO_ERR_CUDA, "parameter upload failed");
     static const int conFields[] = {MYO_F_NCON, MYO_F_NEFC, MYO_F_SOLVER_NITER, MYO_F_CONTACT_GEOM, MYO_F_CONTACT_DIM, MYO_F_CONTACT_EFC_ADDRESS,
                                     MYO_F_CONTACT_DIST, MYO_F_CONTACT_POS, MYO_F_CONTACT_FRAME, MYO_F_CONTACT_INCLUDEMARGIN, MYO_F_CONTACT_FRICTION,
                                     MYO_F_CONTACT_SOLREF, MYO_F_CONTACT_SOLIMP, MYO_F_EFC_J, MYO_F_EFC_POS, MYO_F_EFC_MARGIN, MYO_F_EFC_D,
@@ -236,6 +241,17 @@ static int launchPhases(myo_batch* b, int nsub, int forward_only, const int32_t*
     return r;
   };
   bool ok = true;
+  // mj_collision = broad phase + closed-form pairs, the listed convex pairs one per lane, ordered compaction
+  auto collide = [&](int fslot) {
+    bool r = true;
+    if (b->D.npair > 0 && b->D.nmprpair > 0) r &= cudaMemsetAsync(b->X.mpr_count, 0, sizeof(int), (cudaStream_t)cur) == cudaSuccess;
+    r &= tile(MYO_K_COLLIDE, fslot, 0) == 0;
+    if (b->D.npair > 0) {
+      if (b->D.nmprpair > 0) r &= tile(MYO_K_COLLIDE_MPR, fslot, 0) == 0;
+      r &= tile(MYO_K_COLLIDE_COMPACT, fslot, 0) == 0;
+    }
+    return r;
+  };
   static const int debug_stop = getenv("MYO_DEBUG_STOP") ? atoi(getenv("MYO_DEBUG_STOP")) : -1;   // developer knob: end the pipeline after this many kernels
   int nk = 0;
 #define STOP_HERE() if (debug_stop >= 0 && ++nk >= debug_stop) break
@@ -251,14 +267,14 @@ static int launchPhases(myo_batch* b, int nsub, int forward_only, const int32_t*
       ok &= cudaStreamWaitEvent(S(0), E(0), 0) == cudaSuccess && cudaStreamWaitEvent(S(1), E(0), 0) == cudaSuccess;
       cur = b->side[0]; ok &= tile(MYO_K_TENDON, fslot, 0) == 0;
       cur = b->side[1]; ok &= tile(MYO_K_INERTIA, fslot, forward_only ? 0 : 1) == 0;
-      cur = stream;     ok &= tile(MYO_K_COLLIDE, fslot, 0) == 0;
+      cur = stream;     ok &= collide(fslot);
       ok &= cudaEventRecord(E(1), S(0)) == cudaSuccess && cudaEventRecord(E(2), S(1)) == cudaSuccess;
       ok &= cudaStreamWaitEvent((cudaStream_t)stream, E(1), 0) == cudaSuccess && cudaStreamWaitEvent((cudaStream_t)stream, E(2), 0) == cudaSuccess;
     } else {
       ok &= tile(MYO_K_TENDON, fslot, 0) == 0; STOP_HERE();
       if (!posvel) {
         ok &= tile(MYO_K_INERTIA, fslot, forward_only ? 0 : 1) == 0; STOP_HERE();
-        ok &= tile(MYO_K_COLLIDE, fslot, 0) == 0; STOP_HERE();
+        ok &= collide(fslot); STOP_HERE();
       }
     }
     ok &= tile(MYO_K_VELACT, fslot, posvel ? 1 : 0) == 0; STOP_HERE();

@@ -27,7 +27,7 @@
 #define GRAD_NOISE 2e-6f   // float32 noise floor of the Newton gradient relative to the magnitude of its terms
 #endif
 #define TEAM (t.nw)   // item stride of a loop = the NW warps of the tile's CTA (NW = blockDim.x / 32, a launch parameter)
-struct TParams { DevModel D; SmemLayout L; FieldPtrs F; };
+struct TParams { DevModel D; SmemLayout L; FieldPtrs F; TileAux X; };
 #define MYO_NSLOT 8
 __constant__ TParams tP[MYO_NSLOT + 1];   // slot MYO_NSLOT stays zero: "materialise nothing" (inner substeps)
 namespace {
@@ -1196,7 +1196,9 @@ __device__ __noinline__ void writeConstraintOutputs(int slot, int fslot, SP sm, 
 // Sum of a per-item partial over the items of a world: the partials of the NW warps meet in shared memory and every warp
 // adds them in the same (warp) order, so all warps of a tile hold bit-identical totals and take the same branches; must
 // be called in CTA-uniform control flow.
-#define MAXW 16   // warps per tile CTA (blockDim <= 512)
+#ifndef MAXW
+#define MAXW 8   // warps per tile CTA (blockDim <= 32 MAXW)
+#endif
 __device__ __noinline__ float tileSum(Tm t, float v) {
   __shared__ float red[MAXW][32];
   const int lane = threadIdx.x & 31;

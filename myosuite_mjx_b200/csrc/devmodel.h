@@ -31,7 +31,7 @@ struct DevModel {
   const float *sens_size;                      // [nsensor,3]
   int nframe, nlevel, nroot, ndlevel;
   int nunit, nslot, nentry, nnz;
-  int ncg, npair, neq, nlimj, nlimt;
+  int ncg, npair, nmprpair, neq, nlimj, nlimt;   // nmprpair: candidate pairs whose types need the convex narrow phase
   int nldlop;
   int nconmax, njmax, maxbase;
   // ---- options
@@ -122,10 +122,17 @@ struct SmemLayout {
   // overlay region A (tendon stage)
   int slots, ulen, uwrap, uwpt, gpre, upts, tmpbody;
   // overlay region B (collision / constraint / solver stage)
-  int cgpose, con, conJ, conU, conW, efc, H, nvec, limrow, basev, cand;
+  int cgpose, con, conJ, conU, conW, efc, H, nvec, limrow, basev, cand, ctmp;
   int nv;        // copy of DevModel.nv (the launch sizes the shared-memory Hessian tiles from it)
   int hshared;   // set by the kernel variant at upload: Newton Hessian tiles live in shared memory
   int wantw;     // set at upload: a path-point field is bound, the tendon stage keeps tangent points and wrap counts
+};
+
+// batch-owned work buffers the kernels need besides the scratch
+struct TileAux {
+  int2* mpr_list;   // (world, survivor position) of the candidate pairs that need the convex narrow phase this pass
+  int* mpr_count;   // entries appended so far (zeroed before every collision pass)
+  int mpr_cap;
 };
 
 #endif  // MYO_DEVMODEL_H_

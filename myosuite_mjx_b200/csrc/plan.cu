@@ -558,6 +558,12 @@ void myo_build_plan(const myo_model_desc& m, int nconmax_req, int njmax_req, Dev
       D.sens_site = upload(ss, owned); D.sens_body = upload(sb, owned); D.sens_type = upload(st, owned); D.sens_size = upload(sz, owned);
     }
     D.ncg = (int)cg_geom.size(); D.npair = (int)p1.size();
+    D.nmprpair = 0;
+    for (size_t i = 0; i < p1.size(); i++) {   // same rule as tile.cu isMprPair
+      const int t1 = cg_type[p1[i]], t2 = cg_type[p2[i]];
+      const bool simple1 = t1 == G_SPHERE || t1 == G_CAPSULE, simple2 = t2 == G_SPHERE || t2 == G_CAPSULE;
+      if (t1 != G_PLANE && !(simple1 && simple2 && !(t1 == G_CAPSULE && t2 == G_SPHERE))) D.nmprpair++;
+    }
     D.cg_geom = upload(cg_geom, owned); D.cg_type = upload(cg_type, owned); D.cg_frame = upload(cg_frame, owned); D.cg_body = upload(cg_body, owned);
     D.cg_lpos = upload(cg_lpos, owned); D.cg_lmat = upload(cg_lmat, owned); D.cg_size = upload(cg_size, owned); D.cg_rbound = upload(cg_rbound, owned);
     D.cg_invweight = upload(cg_invw, owned); D.pair_cg1 = upload(p1, owned); D.pair_cg2 = upload(p2, owned); D.pair_dim = upload(pdim, owned);
@@ -656,7 +662,7 @@ void myo_make_layout(DevModel& D, int nconmax_req, int njmax_req, SmemLayout& L)
   L.cgpose = take(12 * D.ncg); L.con = take(12 * D.nconmax); L.conJ = take(nb * D.nconmax * nv); L.efc = take(10 * D.njmax);
   // H: lower triangle + the factor's diagonal (tile.cu newtonKernel when its block does not fit shared memory)
   L.H = take(nv * nv + nv); L.nvec = take(6 * nv); L.limrow = take(2 * (D.nlimj + D.nlimt)); L.basev = take(2 * nb * D.nconmax);
-  L.cand = take(D.npair);
+  L.cand = take(D.npair); L.ctmp = take(16 * D.npair);   // survivor list and per-survivor narrow-phase records
   L.conU = take(nb * D.nconmax * nv);   // W Jb of the Newton Hessian (tile.cu hessianTile)
   L.conW = take(8 * D.nconmax);         // per-contact weights of the active pyramid rows in base-row space
   int endB = o;

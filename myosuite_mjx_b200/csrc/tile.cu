@@ -12,6 +12,30 @@
 // One mj_step = kin -> tendon -> inertia -> collide -> velact -> newton -> conout -> finish   (api.cu).
 #include "common.cuh"
 
+#ifndef MINB_KIN
+#define MINB_KIN 2
+#endif
+#ifndef MINB_TENDON
+#define MINB_TENDON 2
+#endif
+#ifndef MINB_INERTIA
+#define MINB_INERTIA 2
+#endif
+#ifndef MINB_VELACT
+#define MINB_VELACT 2
+#endif
+#ifndef MINB_COLLIDE
+#define MINB_COLLIDE 2
+#endif
+#ifndef MINB_NEWTON
+#define MINB_NEWTON 2
+#endif
+#ifndef MINB_FINISH
+#define MINB_FINISH 2
+#endif
+#ifndef SYRK_UNROLL
+#define SYRK_UNROLL 2   // -6 % step time against the compiler's own choice (profiles/r2_ab.txt)
+#endif
 namespace {
 
 enum { KIN_LOAD = 1, KIN_RESET = 2, KIN_CHECK = 4 };
@@ -31,7 +55,7 @@ __device__ __forceinline__ Ctx tileCtx(int slot, int nworld, const int* mask, fl
 }
 
 // ------------------------------------------------------------------------------------------ kin: state in, mj_kinematics, mj_comPos
-__global__ void __launch_bounds__(512) kinKernel(int slot, int fslot, int nworld, const int* __restrict__ mask, int flags,
+__global__ void __launch_bounds__(32 * MAXW, MINB_KIN) kinKernel(int slot, int fslot, int nworld, const int* __restrict__ mask, int flags,
                                                  float* __restrict__ scratch) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L; const FieldPtrs& F = tP[slot].F;
   Ctx c = tileCtx(slot, nworld, mask, scratch);
@@ -79,14 +103,14 @@ __global__ void __launch_bounds__(512) kinKernel(int slot, int fslot, int nworld
 }
 
 // ------------------------------------------------------------------------------------------ tendon: mj_tendon (+ path points)
-__global__ void __launch_bounds__(512) tendonKernel(int slot, int fslot, int nworld, const int* __restrict__ mask, float* __restrict__ scratch) {
+__global__ void __launch_bounds__(32 * MAXW, MINB_TENDON) tendonKernel(int slot, int fslot, int nworld, const int* __restrict__ mask, float* __restrict__ scratch) {
   Ctx c = tileCtx(slot, nworld, mask, scratch);
   if (!c.live) return;
   tendons(slot, fslot, c.sm, c.t, c.W);
 }
 
 // ------------------------------------------------------------------------------------------ inertia: mj_crb, mj_factorM (+ Euler's M + h B factor)
-__global__ void __launch_bounds__(512) inertiaKernel(int slot, int fslot, int nworld, const int* __restrict__ mask, int euler,
+__global__ void __launch_bounds__(32 * MAXW, MINB_INERTIA) inertiaKernel(int slot, int fslot, int nworld, const int* __restrict__ mask, int euler,
                                                      float* __restrict__ scratch) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
   Ctx c = tileCtx(slot, nworld, mask, scratch);
@@ -103,7 +127,7 @@ __global__ void __launch_bounds__(512) inertiaKernel(int slot, int fslot, int nw
 }
 
 // ------------------------------------------------------------------------------------------ velact: mj_fwdVelocity, mj_fwdActuation, mj_fwdAcceleration
-__global__ void __launch_bounds__(512) velactKernel(int slot, int fslot, int nworld, const int* __restrict__ mask, int posvel,
+__global__ void __launch_bounds__(32 * MAXW, MINB_VELACT) velactKernel(int slot, int fslot, int nworld, const int* __restrict__ mask, int posvel,
                                                     float* __restrict__ scratch) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
   Ctx c = tileCtx(slot, nworld, mask, scratch);
@@ -145,18 +169,25 @@ __device__ __forceinline__ bool broadPass(const DevModel& D, const SmemLayout& L
   const float r = D.cg_rbound[c1] + D.cg_rbound[c2] + margin;
   return !(dot(d, d) > r * r);
 }
-__device__ __forceinline__ int warpMax(int v) { return __reduce_max_sync(__activemask(), v); }
 
-__global__ void __launch_bounds__(512) collideKernel(int slot, int nworld, const int* __restrict__ mask, float* __restrict__ scratch) {
-  const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
+__device__ __forceinline__ bool isMprPair(const DevModel& D, int pr) {
+  const int t1 = D.cg_type[D.pair_cg1[pr]], t2 = D.cg_type[D.pair_cg2[pr]];
+  return t1 != G_PLANE && !((t1 == G_SPHERE || t1 == G_CAPSULE) && (t2 == G_SPHERE || t2 == G_CAPSULE) && !(t1 == G_CAPSULE && t2 == G_SPHERE));
+}
+// collide A: geom poses, broad phase (ordered survivor list per lane), closed-form narrow phase.  Survivors that need the
+// convex narrow phase (MPR: float64, long, data-dependent) are appended to a batch-wide work list instead: a tile has a
+// handful of them per world at different survivor positions, so inside the tile they would run at a few active lanes
+// while the other warps wait; collideMprKernel runs them one pair per LANE.  Per-survivor result record in L.ctmp:
+// 16 floats = hit count, up to two hits (dist, pos, normal).
+__global__ void __launch_bounds__(32 * MAXW, MINB_COLLIDE) collideKernel(int slot, int nworld, const int* __restrict__ mask, float* __restrict__ scratch) {
+  const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L; const TileAux& X = tP[slot].X;
   Ctx c = tileCtx(slot, nworld, mask, scratch);
   if (!c.live) return;
   SP sm = c.sm; Tm t = c.t;
   const int lane = threadIdx.x & 31, nw = t.nw;
   __shared__ int sCnt[MAXW][32];
-  __shared__ int sNm[32];
   if (D.npair == 0 || (D.disableflags & (DSBL_CONTACT | DSBL_CONSTRAINT))) {
-    if (t.tl == 0) sm[L.counts] = __int_as_float(0);
+    if (t.tl == 0) { sm[L.counts] = __int_as_float(0); sm[L.counts + 3] = __int_as_float(0); }
     return;
   }
   TFOR(g, D.ncg) {
@@ -182,65 +213,83 @@ __global__ void __launch_bounds__(512) collideKernel(int slot, int nworld, const
     for (int pr = p0; pr < p1; pr++) if (broadPass(D, L, sm, pr)) cand[off++] = pr;
     TSYNC();
   }
-  // ---- narrow phase.  Per-survivor results live in the solver's scratch (unused until makeConstraint): 16 floats =
-  // count, two hits, one MPR-list slot.
-  auto tmp = sm + L.conJ;
-  const int cap = max(1, (L.limrow - L.conJ) / 16);
-  const int maxcand = warpMax(ncand);
-  int ncon = 0;
-  for (int c0 = 0; c0 < maxcand; c0 += cap) {   // one round unless a world has more survivors than the scratch holds
-    const int cn = max(0, min(cap, ncand - c0));
-    if (t.tl == 0) sNm[lane] = 0;
-    TSYNC();
-    for (int k = t.tl; k < cn; k += nw) {   // closed-form pairs; MPR pairs are only listed
-      const int pr = cand[c0 + k];
-      const int t1 = D.cg_type[D.pair_cg1[pr]], t2 = D.cg_type[D.pair_cg2[pr]];
-      const bool mp = t1 != G_PLANE && !((t1 == G_SPHERE || t1 == G_CAPSULE) && (t2 == G_SPHERE || t2 == G_CAPSULE) && !(t1 == G_CAPSULE && t2 == G_SPHERE));
-      if (!mp) {
-        Hit h[2];
-        const int n = collidePair(slot, sm, pr, h);
-        auto o = tmp + 16 * k;
-        o[0] = __int_as_float(n);
-        for (int q = 0; q < n; q++) { o[1 + 7 * q] = h[q].dist; st3(o + 2 + 7 * q, h[q].pos); st3(o + 5 + 7 * q, h[q].nrm); }
-      } else {
-        const int i = atomicAdd(&sNm[lane], 1);   // list order is irrelevant: results go to the survivor's own record
-        tmp[16 * i + 15] = __int_as_float(k);
-      }
-    }
-    TSYNC();
-    const int nm = sNm[lane];
-    for (int i = t.tl; i < nm; i += nw) {
-      const int k = __float_as_int(tmp[16 * i + 15]);
+  if (t.tl == 0) sm[L.counts + 3] = __int_as_float(ncand);
+  // ---- narrow phase of the closed-form pairs; MPR pairs go to the work list (one atomic per warp and survivor position)
+  auto tmp = sm + L.ctmp;
+  const int w = (int)c.W.w;
+  for (int k = t.tl; k < ncand; k += nw) {
+    const int pr = cand[k];
+    const bool mp = isMprPair(D, pr);
+    if (!mp) {
       Hit h[2];
-      const int n = collidePair(slot, sm, cand[c0 + k], h);
+      const int n = collidePair(slot, sm, pr, h);
       auto o = tmp + 16 * k;
       o[0] = __int_as_float(n);
-      if (n) { o[1] = h[0].dist; st3(o + 2, h[0].pos); st3(o + 5, h[0].nrm); }
+      for (int q = 0; q < n; q++) { o[1 + 7 * q] = h[q].dist; st3(o + 2 + 7 * q, h[q].pos); st3(o + 5 + 7 * q, h[q].nrm); }
     }
-    TSYNC();
-    // in-order compaction of the hits
-    const int kc = (warpMax(cn) + nw - 1) / nw, k0 = t.tl * kc, k1 = min(cn, k0 + kc);
-    int cnt = 0;
-    for (int k = k0; k < k1; k++) cnt += __float_as_int(tmp[16 * k]);
-    sCnt[t.tl][lane] = cnt;
-    TSYNC();
-    int at = ncon, total = 0;
-    for (int j = 0; j < nw; j++) { const int v = sCnt[j][lane]; if (j < t.tl) at += v; total += v; }
-    for (int k = k0; k < k1; k++) {
-      const int n = __float_as_int(tmp[16 * k]);
-      for (int q = 0; q < n; q++, at++) {
-        if (at >= D.nconmax) continue;
-        const int pr = cand[c0 + k];
-        auto cr = sm + L.con + 12 * at; auto o = tmp + 16 * k + 1 + 7 * q;
-        for (int e = 0; e < 7; e++) cr[e] = o[e];
-        cr[7] = __int_as_float(pr); cr[8] = __int_as_float(-1); cr[9] = __int_as_float(D.pair_dim[pr]);
-        // dofs that move exactly one of the two bodies (static per pair): the only non-zero columns of the contact's rows
-        const int f1 = D.cg_frame[D.pair_cg1[pr]], f2 = D.cg_frame[D.pair_cg2[pr]];
-        cr[10] = __int_as_float(D.fr_mask[2 * f1] ^ D.fr_mask[2 * f2]); cr[11] = __int_as_float(D.fr_mask[2 * f1 + 1] ^ D.fr_mask[2 * f2 + 1]);
+    const unsigned act = __activemask();
+    const unsigned mm = __ballot_sync(act, mp);
+    if (mm) {
+      const int leader = __ffs(mm) - 1;
+      int base = 0;
+      if (lane == leader) base = atomicAdd(X.mpr_count, __popc(mm));
+      base = __shfl_sync(act, base, leader);
+      if (mp) {
+        const int at = base + __popc(mm & ((1u << lane) - 1u));
+        if (at < X.mpr_cap) X.mpr_list[at] = make_int2(w, k);
       }
     }
-    ncon += total;
-    TSYNC();
+  }
+}
+// collide MPR: one listed (world, survivor) pair per lane, all lanes busy; the result goes to the survivor's own record, so
+// the (atomic) order of the list does not matter
+__global__ void __launch_bounds__(128) collideMprKernel(int slot, float* __restrict__ scratch) {
+  const SmemLayout& L = tP[slot].L; const TileAux& X = tP[slot].X;
+  const int n = min(*X.mpr_count, X.mpr_cap);
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const int2 e = X.mpr_list[i];
+    SP sm; sm.p = scratch + (size_t)(e.x >> 5) * L.total * SCR + (e.x & 31);
+    const int pr = __float_as_int(sm[L.cand + e.y]);
+    Hit h[2];
+    const int nh = collidePair(slot, sm, pr, h);
+    auto o = sm + L.ctmp + 16 * e.y;
+    o[0] = __int_as_float(nh);
+    if (nh) { o[1] = h[0].dist; st3(o + 2, h[0].pos); st3(o + 5, h[0].nrm); }
+  }
+}
+// collide B: in-order compaction of the hits into contact records -- contact order (hence geom1 / geom2 / efc_address) is
+// MuJoCo's
+__global__ void __launch_bounds__(32 * MAXW, 2) collideCompactKernel(int slot, int nworld, const int* __restrict__ mask, float* __restrict__ scratch) {
+  const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
+  Ctx c = tileCtx(slot, nworld, mask, scratch);
+  const unsigned lmask = __ballot_sync(0xffffffffu, c.live);
+  if (!c.live) return;
+  SP sm = c.sm; Tm t = c.t;
+  const int lane = threadIdx.x & 31, nw = t.nw;
+  __shared__ int sCnt[MAXW][32];
+  if (D.npair == 0 || (D.disableflags & (DSBL_CONTACT | DSBL_CONSTRAINT))) return;
+  SPI cand = asInt(sm + L.cand);
+  auto tmp = sm + L.ctmp;
+  const int ncand = __float_as_int(sm[L.counts + 3]);
+  const int kc = (__reduce_max_sync(lmask, ncand) + nw - 1) / nw, k0 = min(ncand, t.tl * kc), k1 = min(ncand, k0 + kc);
+  int cnt = 0;
+  for (int k = k0; k < k1; k++) cnt += __float_as_int(tmp[16 * k]);
+  sCnt[t.tl][lane] = cnt;
+  TSYNC();
+  int at = 0, ncon = 0;
+  for (int j = 0; j < nw; j++) { const int v = sCnt[j][lane]; if (j < t.tl) at += v; ncon += v; }
+  for (int k = k0; k < k1; k++) {
+    const int n = __float_as_int(tmp[16 * k]);
+    for (int q = 0; q < n; q++, at++) {
+      if (at >= D.nconmax) continue;
+      const int pr = cand[k];
+      auto cr = sm + L.con + 12 * at; auto o = tmp + 16 * k + 1 + 7 * q;
+      for (int e = 0; e < 7; e++) cr[e] = o[e];
+      cr[7] = __int_as_float(pr); cr[8] = __int_as_float(-1); cr[9] = __int_as_float(D.pair_dim[pr]);
+      // dofs that move exactly one of the two bodies (static per pair): the only non-zero columns of the contact's rows
+      const int f1 = D.cg_frame[D.pair_cg1[pr]], f2 = D.cg_frame[D.pair_cg2[pr]];
+      cr[10] = __int_as_float(D.fr_mask[2 * f1] ^ D.fr_mask[2 * f2]); cr[11] = __int_as_float(D.fr_mask[2 * f1 + 1] ^ D.fr_mask[2 * f2 + 1]);
+    }
   }
   if (t.tl == 0) {
     if (ncon > D.nconmax) {
@@ -534,6 +583,7 @@ __device__ __noinline__ void hessianTile(int slot, SP sm, Tm t, SP H, SP Hd, int
 #pragma unroll
         for (int b = 0; b < 4; b++) acc[a][b] = 0.f;
       auto Ub = sm + L.conU; auto Jb = sm + L.conJ;
+      TFOR_PRAGMA(SYRK_UNROLL)
       for (int i = 0; i < nbase; i++) {
         float u[4], j[4];
 #pragma unroll
@@ -751,7 +801,7 @@ __device__ __noinline__ int newtonTile(int slot, SP sm, Tm t, const NewtonMem& M
 // model's block does not fit (nv beyond ~55), the same kernel runs with everything in the world's scratch column.
 static inline size_t newtonSmemFloats(int nv) { return (size_t)(TRI(nv) + 7 * nv) * 32; }
 #define NEWTON_SMEM_MAX (190 * 1024)   // + ~31 KB of static reduction / scan buffers <= 227 KB per CTA
-__global__ void __launch_bounds__(512) newtonKernel(int slot, int fslot, int nworld, const int* __restrict__ mask, int check_acc,
+__global__ void __launch_bounds__(32 * MAXW, MINB_NEWTON) newtonKernel(int slot, int fslot, int nworld, const int* __restrict__ mask, int check_acc,
                                                     int use_smem, float* __restrict__ scratch) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
   extern __shared__ float tileShared[];
@@ -811,7 +861,7 @@ __global__ void __launch_bounds__(512) newtonKernel(int slot, int fslot, int nwo
 // ------------------------------------------------------------------------------------------ finish: mj_Euler, state out
 // mj_Euler with implicit joint damping (the factor of M + h B comes from inertiaKernel), quaternion integration on the
 // manifold; then the state and the per-dof results of the solve go out as full lines.
-__global__ void __launch_bounds__(512) finishKernel(int slot, int fslot, int nworld, const int* __restrict__ mask, int flags,
+__global__ void __launch_bounds__(32 * MAXW, MINB_FINISH) finishKernel(int slot, int fslot, int nworld, const int* __restrict__ mask, int flags,
                                                     float* __restrict__ scratch) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L; const FieldPtrs& F = tP[slot].F;
   Ctx c = tileCtx(slot, nworld, mask, scratch);
@@ -908,19 +958,19 @@ __global__ void quatKatKernel(int n, const float* __restrict__ qa, const float* 
 }  // namespace
 
 // ---------------------------------------------------------------------------------------------- host side
-int myo_tile_upload(int slot, const DevModel& D, const SmemLayout& L, const FieldPtrs& F, void* stream) {
+int myo_tile_upload(int slot, const DevModel& D, const SmemLayout& L, const FieldPtrs& F, const TileAux& X, void* stream) {
   static TParams staging[MYO_NSLOT];   // must outlive the async copy
   if (slot < 0 || slot >= MYO_NSLOT) return -1;
   TParams& P = staging[slot];
-  P.D = D; P.L = L; P.F = F;
+  P.D = D; P.L = L; P.F = F; P.X = X;
   return cudaMemcpyToSymbolAsync(tP, &P, sizeof(TParams), (size_t)slot * sizeof(TParams), cudaMemcpyHostToDevice, (cudaStream_t)stream) == cudaSuccess ? 0 : -1;
 }
 static int envInt(const char* name, int dflt) { const char* e = getenv(name); return e ? atoi(e) : dflt; }
 // Warps per tile of each kernel (developer knobs MYO_NW_*): enough warps per SM to hide the scratch latency, few enough
 // that the item loops still have work for every warp.
 int myo_tile_launch(int kernel, int slot, int fslot, int nworld, const int* mask, int flags, float* scratch, void* stream) {
-  static const int nwKin = envInt("MYO_NW_KIN", 16), nwTen = envInt("MYO_NW_TEN", 16), nwIne = envInt("MYO_NW_INE", 8),
-                   nwCol = envInt("MYO_NW_COL", 16), nwVel = envInt("MYO_NW_VEL", 8), nwFin = envInt("MYO_NW_FIN", 8),
+  static const int nwKin = envInt("MYO_NW_KIN", 8), nwTen = envInt("MYO_NW_TEN", 8), nwIne = envInt("MYO_NW_INE", 8),
+                   nwCol = envInt("MYO_NW_COL", 8), nwVel = envInt("MYO_NW_VEL", 8), nwFin = envInt("MYO_NW_FIN", 8),
                    nwOut = envInt("MYO_NW_OUT", 8), yOut = envInt("MYO_Y_OUT", 4), nwNew = envInt("MYO_NW_NEWTON", 8);
   const int tiles = (nworld + 31) / 32;
   cudaStream_t st = (cudaStream_t)stream;
@@ -929,6 +979,8 @@ int myo_tile_launch(int kernel, int slot, int fslot, int nworld, const int* mask
     case MYO_K_TENDON: tendonKernel<<<tiles, 32 * nwTen, 0, st>>>(slot, fslot, nworld, mask, scratch); break;
     case MYO_K_INERTIA: inertiaKernel<<<tiles, 32 * nwIne, 0, st>>>(slot, fslot, nworld, mask, flags, scratch); break;
     case MYO_K_COLLIDE: collideKernel<<<tiles, 32 * nwCol, 0, st>>>(slot, nworld, mask, scratch); break;
+    case MYO_K_COLLIDE_MPR: collideMprKernel<<<148 * 4, 128, 0, st>>>(slot, scratch); break;
+    case MYO_K_COLLIDE_COMPACT: collideCompactKernel<<<tiles, 32 * nwCol, 0, st>>>(slot, nworld, mask, scratch); break;
     case MYO_K_VELACT: velactKernel<<<tiles, 32 * nwVel, 0, st>>>(slot, fslot, nworld, mask, flags, scratch); break;
     case MYO_K_FINISH: finishKernel<<<tiles, 32 * nwFin, 0, st>>>(slot, fslot, nworld, mask, flags, scratch); break;
     case MYO_K_NEWTON: {

@@ -8,7 +8,7 @@ import subprocess
 from . import desc as _desc
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libmyostep.so")
+LIB_PATH = os.environ.get("MYO_LIB") or os.path.join(_HERE, "libmyostep.so")   # MYO_LIB: developer knob (A/B builds)
 
 
 class MyoError(RuntimeError):
