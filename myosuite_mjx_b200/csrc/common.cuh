@@ -1197,7 +1197,7 @@ __device__ __noinline__ void writeConstraintOutputs(int slot, int fslot, SP sm, 
 // adds them in the same (warp) order, so all warps of a tile hold bit-identical totals and take the same branches; must
 // be called in CTA-uniform control flow.
 #ifndef MAXW
-#define MAXW 8   // warps per tile CTA (blockDim <= 32 MAXW)
+#define MAXW 12   // warps per tile CTA (blockDim <= 32 MAXW); with two CTAs per SM the kernels get <= 85 registers
 #endif
 __device__ __noinline__ float tileSum(Tm t, float v) {
   __shared__ float red[MAXW][32];
@@ -1242,13 +1242,19 @@ __device__ __noinline__ void setRow(int slot, SP sm, int r, int type, int id, fl
 __device__ __noinline__ void baseMul(int slot, SP sm, Tm t, int ncon, SP x, SP out) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
   const int nbr = D.maxbase * ncon, nv = D.nv;
-  TFOR(b, nbr) {
-    auto J = sm + L.conJ + b * nv;
-    float a0 = 0.f, a1 = 0.f;
+  // two rows per pass (they share the loads of x), two accumulators each: the dot products are latency-bound
+  for (int b = t.tl; b < nbr; b += 2 * TEAM) {
+    const int b2 = b + TEAM;
+    auto J0 = sm + L.conJ + b * nv; auto J1 = sm + L.conJ + min(b2, nbr - 1) * nv;
+    float a0 = 0.f, a1 = 0.f, c0 = 0.f, c1 = 0.f;
     int k = 0;
-    for (; k + 1 < nv; k += 2) { a0 = fmaf(J[k], x[k], a0); a1 = fmaf(J[k + 1], x[k + 1], a1); }
-    if (k < nv) a0 = fmaf(J[k], x[k], a0);
+    for (; k + 1 < nv; k += 2) {
+      const float x0 = x[k], x1 = x[k + 1];
+      a0 = fmaf(J0[k], x0, a0); a1 = fmaf(J0[k + 1], x1, a1); c0 = fmaf(J1[k], x0, c0); c1 = fmaf(J1[k + 1], x1, c1);
+    }
+    if (k < nv) { const float x0 = x[k]; a0 = fmaf(J0[k], x0, a0); c0 = fmaf(J1[k], x0, c0); }
     out[b] = a0 + a1;
+    if (b2 < nbr) out[b2] = c0 + c1;
   }
 }
 // J_r . x for one efc row (bx = base products of x)
@@ -1299,42 +1305,61 @@ __device__ __noinline__ void constraintForce(int slot, SP sm, Tm t, int ncon, in
   TFOR(r, nefc) { const float jar = EFC(E_JAR, r); EFC(E_FORCE, r) = rowOn(EFCI(E_DESC0, r), jar) ? -EFC(E_D, r) * jar : 0.f; }
   TSYNC();
   auto bf = sm + L.basev + nb * D.nconmax;
-  TFOR(b, nb * ncon) {
-    const int c = b / nb, k = b - c * nb;
+  TFOR(c, ncon) {   // base-row forces of one contact from its pyramid rows (mju_decodePyramid, transposed)
     auto cr = sm + L.con + 12 * c;
     const int adr = __float_as_int(cr[8]), dim = __float_as_int(cr[9]);
-    float f = 0.f;
-    if (adr >= 0 && k < dim) {
-      if (dim == 1) f = EFC(E_FORCE, adr);
-      else if (k == 0) { for (int p = 0; p < 2 * (dim - 1); p++) f += EFC(E_FORCE, adr + p); }
-      else f = EFC(E_COEF, adr + 2 * (k - 1)) * (EFC(E_FORCE, adr + 2 * (k - 1)) - EFC(E_FORCE, adr + 2 * (k - 1) + 1));
+    float fb[4] = {0.f, 0.f, 0.f, 0.f};
+    if (adr >= 0) {
+      if (dim == 1) fb[0] = EFC(E_FORCE, adr);
+      else
+        for (int k = 1; k < dim; k++) {
+          const float fp = EFC(E_FORCE, adr + 2 * (k - 1)), fm = EFC(E_FORCE, adr + 2 * (k - 1) + 1);
+          fb[0] += fp + fm; fb[k] = EFC(E_COEF, adr + 2 * (k - 1)) * (fp - fm);
+        }
     }
-    bf[b] = f;
+    for (int k = 0; k < nb; k++) bf[c * nb + k] = fb[k];
   }
   TSYNC();
-  TFOR(k, nv) {
-    float acc = 0.f;
-    for (int e = D.dofeq_start[k]; e < D.dofeq_start[k + 1]; e++) {
-      const int v = D.dofeq_list[e], r = v >> 1;
-      acc += (v & 1) ? EFC(E_COEF, r) * EFC(E_FORCE, r) : EFC(E_FORCE, r);
-    }
-    const int li = D.dof_limidx[k];
-    if (li >= 0)
-      for (int q = 0; q < 2; q++) { const int r = __float_as_int(sm[L.limrow + 2 * li + q]); if (r >= 0) acc += EFC(E_COEF, r) * EFC(E_FORCE, r); }
-    if (D.nlimt > 0)
-      for (int c = D.col_start[k]; c < D.col_start[k + 1]; c++) {
-        const int n = D.col_nz[c], lt = D.ten_limidx[D.nz_tendon[n]];
-        if (lt < 0) continue;
-        for (int q = 0; q < 2; q++) {
-          const int r = __float_as_int(sm[L.limrow + 2 * (D.nlimj + lt) + q]);
-          if (r >= 0) acc += EFC(E_COEF, r) * EFC(E_FORCE, r) * sm[L.tenJ + n];
+  const int nbr = nb * ncon;
+  for (int kb = t.tl; kb < nv; kb += 3 * TEAM) {   // three dofs per pass: they share the loads of bf
+    float res[3];
+    for (int g = 0; g < 3; g++) {
+      const int k = kb + g * TEAM;
+      float acc = 0.f;
+      if (k < nv) {
+        for (int e = D.dofeq_start[k]; e < D.dofeq_start[k + 1]; e++) {
+          const int v = D.dofeq_list[e], r = v >> 1;
+          acc += (v & 1) ? EFC(E_COEF, r) * EFC(E_FORCE, r) : EFC(E_FORCE, r);
         }
+        const int li = D.dof_limidx[k];
+        if (li >= 0)
+          for (int q = 0; q < 2; q++) { const int r = __float_as_int(sm[L.limrow + 2 * li + q]); if (r >= 0) acc += EFC(E_COEF, r) * EFC(E_FORCE, r); }
+        if (D.nlimt > 0)
+          for (int c = D.col_start[k]; c < D.col_start[k + 1]; c++) {
+            const int n = D.col_nz[c], lt = D.ten_limidx[D.nz_tendon[n]];
+            if (lt < 0) continue;
+            for (int q = 0; q < 2; q++) {
+              const int r = __float_as_int(sm[L.limrow + 2 * (D.nlimj + lt) + q]);
+              if (r >= 0) acc += EFC(E_COEF, r) * EFC(E_FORCE, r) * sm[L.tenJ + n];
+            }
+          }
       }
-    float a1 = 0.f;
+      res[g] = acc;
+    }
+    const int k0 = kb, k1 = min(kb + TEAM, nv - 1), k2 = min(kb + 2 * TEAM, nv - 1);
+    auto Jk = sm + L.conJ;
+    float a0 = 0.f, a1 = 0.f, a2 = 0.f, e0 = 0.f, e1 = 0.f, e2 = 0.f;
     int b = 0;
-    for (; b + 1 < nb * ncon; b += 2) { acc = fmaf(sm[L.conJ + b * nv + k], bf[b], acc); a1 = fmaf(sm[L.conJ + (b + 1) * nv + k], bf[b + 1], a1); }
-    if (b < nb * ncon) acc = fmaf(sm[L.conJ + b * nv + k], bf[b], acc);
-    out[k] = acc + a1;
+    for (; b + 1 < nbr; b += 2) {
+      const float f0 = bf[b], f1 = bf[b + 1];
+      auto Ja = Jk + b * nv; auto Jb = Jk + (b + 1) * nv;
+      a0 = fmaf(Ja[k0], f0, a0); a1 = fmaf(Ja[k1], f0, a1); a2 = fmaf(Ja[k2], f0, a2);
+      e0 = fmaf(Jb[k0], f1, e0); e1 = fmaf(Jb[k1], f1, e1); e2 = fmaf(Jb[k2], f1, e2);
+    }
+    if (b < nbr) { const float f0 = bf[b]; auto Ja = Jk + b * nv; a0 = fmaf(Ja[k0], f0, a0); a1 = fmaf(Ja[k1], f0, a1); a2 = fmaf(Ja[k2], f0, a2); }
+    out[k0] = res[0] + a0 + e0;
+    if (kb + TEAM < nv) out[kb + TEAM] = res[1] + a1 + e1;
+    if (kb + 2 * TEAM < nv) out[kb + 2 * TEAM] = res[2] + a2 + e2;
   }
   TSYNC();
 }

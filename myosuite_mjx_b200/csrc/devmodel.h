@@ -122,7 +122,7 @@ struct SmemLayout {
   // overlay region A (tendon stage)
   int slots, ulen, uwrap, uwpt, gpre, upts, tmpbody;
   // overlay region B (collision / constraint / solver stage)
-  int cgpose, con, conJ, conU, conW, efc, H, nvec, limrow, basev, cand, ctmp;
+  int cgpose, con, conJ, conU, conW, efc, H, Hsave, nvec, limrow, basev, cand, ctmp;
   int nv;        // copy of DevModel.nv (the launch sizes the shared-memory Hessian tiles from it)
   int hshared;   // set by the kernel variant at upload: Newton Hessian tiles live in shared memory
   int wantw;     // set at upload: a path-point field is bound, the tendon stage keeps tangent points and wrap counts

@@ -661,7 +661,11 @@ void myo_make_layout(DevModel& D, int nconmax_req, int njmax_req, SmemLayout& L)
   // region B: collision, constraints, solver
   L.cgpose = take(12 * D.ncg); L.con = take(12 * D.nconmax); L.conJ = take(nb * D.nconmax * nv); L.efc = take(10 * D.njmax);
   // H: lower triangle + the factor's diagonal (tile.cu newtonKernel when its block does not fit shared memory)
-  L.H = take(nv * nv + nv); L.nvec = take(6 * nv); L.limrow = take(2 * (D.nlimj + D.nlimt)); L.basev = take(2 * nb * D.nconmax);
+  L.H = take(nv * nv + nv);
+  L.Hsave = take(nv * (nv + 1) / 2);   // the unfactored Hessian, updated by the later Newton passes of a tile
+  L.nvec = take(6 * nv);
+  L.limrow = take(2 * (D.nlimj + D.nlimt));
+  L.basev = take(2 * nb * D.nconmax);
   L.cand = take(D.npair); L.ctmp = take(16 * D.npair);   // survivor list and per-survivor narrow-phase records
   L.conU = take(nb * D.nconmax * nv);   // W Jb of the Newton Hessian (tile.cu hessianTile)
   L.conW = take(8 * D.nconmax);         // per-contact weights of the active pyramid rows in base-row space

@@ -488,7 +488,7 @@ __device__ __noinline__ int makeConstraintTile(int slot, SP sm, Tm t, int ncon, 
 // contact's active pyramid rows in base-row space, J^T D J = Jb^T (W Jb) =: Jb^T U, a dense [nv x nbase] x [nbase x nv]
 // product over the tile's nbase = maxbase * nconT base rows, done in 4 x 4 register blocks of H (one block per warp at a
 // time, the warps stream the same rows of U and Jb through L1 together).
-__device__ __noinline__ void hessianTile(int slot, SP sm, Tm t, SP H, SP Hd, int ncon, int nconT, int nefc) {
+__device__ __noinline__ void hessianAssemble(int slot, SP sm, Tm t, SP H, int ncon, int nconT, int nefc) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
   const int nv = D.nv, nb = D.maxbase, nw = t.nw;
   TFOR(i, TRI(nv)) H[i] = 0.f;
@@ -603,7 +603,65 @@ __device__ __noinline__ void hessianTile(int slot, SP sm, Tm t, SP H, SP Hd, int
     }
     TSYNC();
   }
-  // left-looking Cholesky, warps over rows; the diagonal of the factor goes to Hd (H keeps the unscaled pivot)
+  TFOR(i, TRI(nv)) sm[L.Hsave + i] = H[i];   // keep the unfactored matrix: later passes of the tile update it (hessianUpdate)
+}
+// Later Newton passes of a tile: only the rows whose active state flipped in the last line search change H, each by a
+// sparse rank-1 term +-D_r J_r^T J_r (the flags were left in E_JV by the row update).  One warp applies them, every lane
+// walking its own flipped rows -- a few hundred instructions against the dense rebuild's ~10^5.
+__device__ __noinline__ void hessianUpdate(int slot, SP sm, Tm t, SP H, int nefc) {
+  const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
+  const int nv = D.nv, nb = D.maxbase;
+  TFOR(i, TRI(nv)) H[i] = sm[L.Hsave + i];
+  TSYNC();
+  if (t.tl == 0) {
+    for (int r = D.neq; r < nefc; r++) {
+      const float flip = EFC(E_JV, r);
+      if (flip == 0.f) continue;
+      const float s = flip * EFC(E_D, r);
+      const int d0 = EFCI(E_DESC0, r), type = d0 & 3, id = d0 >> 2;
+      const float coef = EFC(E_COEF, r);
+      if (type == ROW_LIMJ) { const int k = D.limj_dof[id]; H[TRI(k) + k] += s; }
+      else if (type == ROW_CON) {
+        const int bt = EFCI(E_DESC1, r), c = id / nb;
+        auto cr = sm + L.con + 12 * c;
+        const unsigned mlo = (unsigned)__float_as_int(cr[10]), mhi = (unsigned)__float_as_int(cr[11]);
+        auto Jn = sm + L.conJ + id * nv; auto Jt = sm + L.conJ + (bt >= 0 ? bt : id) * nv;
+        const float ct = bt >= 0 ? coef : 0.f;
+        for (int half = 0; half < 2; half++) {
+          unsigned wa = half ? mhi : mlo;
+          while (wa) {
+            const int a = 32 * half + __ffs((int)wa) - 1;
+            wa &= wa - 1u;
+            const float ja = s * fmaf(ct, Jt[a], Jn[a]);
+            auto Ha = H + TRI(a);
+            for (int h2 = 0; h2 <= half; h2++) {
+              unsigned wb = h2 ? mhi : mlo;
+              if (h2 == half) wb &= (2u << (a & 31)) - 1u;   // columns up to the diagonal
+              while (wb) {
+                const int b = 32 * h2 + __ffs((int)wb) - 1;
+                wb &= wb - 1u;
+                Ha[b] = fmaf(ja, fmaf(ct, Jt[b], Jn[b]), Ha[b]);
+              }
+            }
+          }
+        }
+      } else if (type == ROW_LIMT) {
+        const int tn = D.limt_ten[id], n0 = D.ten_nzstart[tn], n1 = D.ten_nzstart[tn + 1];
+        for (int a = n0; a < n1; a++)
+          for (int b = n0; b < n1; b++) {
+            const int da = D.nz_dof[a], db = D.nz_dof[b];
+            if (da >= db) H[TRI(da) + db] += s * sm[L.tenJ + a] * sm[L.tenJ + b];   // coef^2 = 1
+          }
+      }
+    }
+  }
+  TSYNC();
+  TFOR(i, TRI(nv)) sm[L.Hsave + i] = H[i];
+}
+// left-looking Cholesky of H in place, warps over rows; the diagonal of the factor goes to Hd (H keeps the unscaled pivot)
+__device__ __noinline__ void choleskyTile(int nv, SP H, SP Hd, Tm t) {
+  const int nw = t.nw;
+  TSYNC();
   for (int j = 0; j < nv; j++) {
     for (int r = j + t.tl; r < nv; r += nw) {
       auto Hr = H + TRI(r); auto Hj = H + TRI(j);
@@ -676,26 +734,31 @@ __device__ __noinline__ int newtonTile(int slot, SP sm, Tm t, const NewtonMem& M
   SP qacc = M.qacc, Ma = M.Ma, grad = M.grad, search = M.search, Mv = M.Mv, tmp = M.tmp;
   auto smooth = sm + L.smooth; auto qas = sm + L.qacc_smooth; auto warm = sm + L.warm;
   const float scale = 1.f / (D.meaninertia * (float)max(1, nv));
-  // warm start: cheaper of qacc_warmstart and qacc_smooth
-  float costW = 3.4e38f;
+  // warm start: cheaper of qacc_warmstart and qacc_smooth.  The warm start is evaluated last, so when every world of the
+  // tile keeps it (the steady state of a rollout) its row residuals, M qacc and cost are already in place.
+  const float costS = residualCost(slot, sm, t, ncon, nefc, qas);
+  float costW = 3.4e38f, gaussW = 0.f;
   if (!(D.disableflags & DSBL_WARMSTART)) {
     mulMsparse(slot, sm + L.qM, warm, Ma, t);
     TSYNC();
     float g = 0.f;
     TFOR(k, nv) g = fmaf(0.5f * (Ma[k] - smooth[k]), warm[k] - qas[k], g);
-    costW = TSUM(g) + residualCost(slot, sm, t, ncon, nefc, warm);
+    gaussW = TSUM(g);
+    costW = gaussW + residualCost(slot, sm, t, ncon, nefc, warm);
   }
-  const float costS = residualCost(slot, sm, t, ncon, nefc, qas);
   const bool useWarm = !(costW > costS);
   TFOR(k, nv) qacc[k] = useWarm ? warm[k] : qas[k];
   TSYNC();
-  mulMsparse(slot, sm + L.qM, qacc, Ma, t);
-  TSYNC();
-  float gauss = 0.f;
-  TFOR(k, nv) gauss = fmaf(0.5f * (Ma[k] - smooth[k]), qacc[k] - qas[k], gauss);
-  gauss = TSUM(gauss);
-  float cost = gauss + residualCost(slot, sm, t, ncon, nefc, qacc);
-  int iter = 0;
+  float gauss = gaussW, cost = costW;
+  if (__ballot_sync(lmask, !useWarm)) {   // tile-uniform: some world starts from qacc_smooth
+    mulMsparse(slot, sm + L.qM, qacc, Ma, t);
+    TSYNC();
+    float g = 0.f;
+    TFOR(k, nv) g = fmaf(0.5f * (Ma[k] - smooth[k]), qacc[k] - qas[k], g);
+    gauss = TSUM(g);
+    cost = gauss + residualCost(slot, sm, t, ncon, nefc, qacc);
+  }
+  int iter = 0, pass = 0;   // pass: Newton passes of the tile so far (tile-uniform)
   bool active = nefc > 0;
   const int lsmax = D.ls_iterations;
   for (;;) {
@@ -713,7 +776,9 @@ __device__ __noinline__ int newtonTile(int slot, SP sm, Tm t, const NewtonMem& M
     if (active && iter > 0 && (scale * gn < D.tolerance || gn < GRAD_NOISE * gr)) active = false;
     if (active && iter >= D.iterations) { *status |= MYO_WORLD_SOLVER_MAXITER; active = false; }
     if (!__ballot_sync(lmask, active)) break;   // the tile is done when its slowest world is
-    hessianTile(slot, sm, t, M.H, M.Hd, ncon, nconT, nefc);
+    if (pass == 0) hessianAssemble(slot, sm, t, M.H, ncon, nconT, nefc); else hessianUpdate(slot, sm, t, M.H, nefc);
+    choleskyTile(nv, M.H, M.Hd, t);
+    pass++;
     cholSolveTile(nv, M.H, M.Hd, search, tmp, t);
     float sn = 0.f;
     TFOR(k, nv) { const float s = -search[k]; search[k] = s; sn = fmaf(s, s, sn); }
@@ -777,8 +842,13 @@ __device__ __noinline__ int newtonTile(int slot, SP sm, Tm t, const NewtonMem& M
     if (active) TFOR(k, nv) { qacc[k] = fmaf(alpha, search[k], qacc[k]); Ma[k] = fmaf(alpha, Mv[k], Ma[k]); }
     float gc[2] = {0.f, 0.f};
     for (int r = t.tl; r < nefc; r += nw) {
-      float jar = EFC(E_JAR, r);
-      if (active) { jar = fmaf(alpha, EFC(E_JV, r), jar); EFC(E_JAR, r) = jar; }
+      float jar = EFC(E_JAR, r), flip = 0.f;
+      if (active) {
+        const float old = jar;
+        jar = fmaf(alpha, EFC(E_JV, r), jar); EFC(E_JAR, r) = jar;
+        flip = (jar < 0.f ? 1.f : 0.f) - (old < 0.f ? 1.f : 0.f);   // the row joins (+1) or leaves (-1) the active set: hessianUpdate
+      }
+      EFC(E_JV, r) = flip;
       if (rowOn(EFCI(E_DESC0, r), jar)) gc[1] = fmaf(0.5f * EFC(E_D, r) * jar, jar, gc[1]);
     }
     TSYNC();
@@ -969,9 +1039,13 @@ static int envInt(const char* name, int dflt) { const char* e = getenv(name); re
 // Warps per tile of each kernel (developer knobs MYO_NW_*): enough warps per SM to hide the scratch latency, few enough
 // that the item loops still have work for every warp.
 int myo_tile_launch(int kernel, int slot, int fslot, int nworld, const int* mask, int flags, float* scratch, void* stream) {
-  static const int nwKin = envInt("MYO_NW_KIN", 8), nwTen = envInt("MYO_NW_TEN", 8), nwIne = envInt("MYO_NW_INE", 8),
-                   nwCol = envInt("MYO_NW_COL", 8), nwVel = envInt("MYO_NW_VEL", 8), nwFin = envInt("MYO_NW_FIN", 8),
-                   nwOut = envInt("MYO_NW_OUT", 8), yOut = envInt("MYO_Y_OUT", 4), nwNew = envInt("MYO_NW_NEWTON", 8);
+  // Measured on 8192 MyoHand worlds (profiles/r2_warps_per_tile.txt): every kernel is bound by the dependent-instruction
+  // latency of its warps, and a tile's warps split its items, so more warps per tile shorten the chains -- until the
+  // register file (two tiles per SM must stay resident: 256 tiles on 148 SMs) forces spills.  12 is the sweet spot for the
+  // solver (8: +6.6 % step time, 10: +3.9 %, 16 at <= 64 registers: +1.8 %); the tendon phase prefers 8.
+  static const int nwKin = envInt("MYO_NW_KIN", 12), nwTen = envInt("MYO_NW_TEN", 8), nwIne = envInt("MYO_NW_INE", 8),
+                   nwCol = envInt("MYO_NW_COL", 12), nwVel = envInt("MYO_NW_VEL", 12), nwFin = envInt("MYO_NW_FIN", 8),
+                   nwOut = envInt("MYO_NW_OUT", 8), yOut = envInt("MYO_Y_OUT", 4), nwNew = envInt("MYO_NW_NEWTON", 12);
   const int tiles = (nworld + 31) / 32;
   cudaStream_t st = (cudaStream_t)stream;
   switch (kernel) {

@@ -4,7 +4,7 @@ import ctypes, os, subprocess, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 NAMES = ("total qpos qvel act ctrl frames xanchor xaxis rootcom cinert crb cdof cdof_dot cvel cacc qM qLD qLDinv qH qHinv tenlen tenvel tenJ actlen actvel "
          "actforce actdot bias passive qfrc_act smooth qfrc_con qacc_smooth qacc warm tmpv tforce counts wstate slots ulen uwrap uwpt gpre upts tmpbody "
-         "cgpose con conJ conU conW efc H nvec limrow basev cand nv hshared wantw").split()
+         "cgpose con conJ conU conW efc H Hsave nvec limrow basev cand ctmp nv hshared wantw").split()
 if len(sys.argv) > 1 and sys.argv[1] == "one":
     sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
     import numpy as np, torch, parity, bench

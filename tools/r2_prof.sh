@@ -6,7 +6,7 @@ skip=${2:-2440}
 out=gpurun_out
 python bench.py --no-cpu --steps 20 --warmup 300 > $out/${tag}_plain.json 2> $out/${tag}_plain.err || { echo "plain run failed"; tail -5 $out/${tag}_plain.err; exit 1; }
 ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum,smsp__issue_active.avg.pct_of_peak_sustained_active,sm__warps_active.avg.per_cycle_active,smsp__thread_inst_executed_per_inst_executed.ratio,smsp__inst_executed.sum \
-  --clock-control none --launch-skip $skip -c 18 --csv --log-file $out/${tag}_launches.csv python bench.py --no-cpu --steps 20 --warmup 300 > $out/${tag}_ncu1.log 2>&1
+  --clock-control none --cache-control none --launch-skip $skip -c 20 --csv --log-file $out/${tag}_launches.csv python bench.py --no-cpu --steps 20 --warmup 300 > $out/${tag}_ncu1.log 2>&1
 if [ "$3" == "full" ]; then
 ncu --set full --import-source on --clock-control none --launch-skip $skip -c 9 -f -o $out/${tag}_full python bench.py --no-cpu --steps 20 --warmup 300 > $out/${tag}_ncu2.log 2>&1
 fi
