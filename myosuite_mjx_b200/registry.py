@@ -61,7 +61,7 @@ def make(env_id, nworld=1, model=None, **overrides):
     fixture, kind, horizon, kwargs = SPECS[env_id]
     if model is None:
         import os
-        model = mjcf.Model.load(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "golden", "models", fixture + ".npz"))
+        model = mjcf.Model.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "models", fixture + ".npz"))
     elif isinstance(model, str):
         model = mjcf.from_xml_path(model)
     kw = ordered_targets(model, kwargs)

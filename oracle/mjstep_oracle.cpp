@@ -31,6 +31,7 @@
 #include <map>
 #include <string>
 #include <limits>
+#include <memory>
 #include <vector>
 
 #include "../include/myostep.h"
@@ -1517,6 +1518,52 @@ int orc_rollout(const myo_model_desc* desc, int nworld, int nsteps, int hold, co
   worker();
   for (auto& t : pool) t.join();
   return 0;
+}
+
+// CPU baseline with state carried across calls (one continuing rollout): a pool of worlds, advanced `nsteps` mj_steps per
+// call on `nthreads` threads, ctrl ~ U[0,1] redrawn every `hold` steps from a per-world stream.
+struct OrcPool { std::vector<std::unique_ptr<OrcD>> w; std::vector<uint64_t> rng; std::vector<int> t; };
+void* orc_pool_create(const myo_model_desc* desc, int nworld, const double* qpos_init, uint64_t seed) {
+  OrcPool* p = new OrcPool();
+  for (int i = 0; i < nworld; i++) {
+    p->w.emplace_back(new OrcD(*desc));
+    OrcD& o = *p->w.back();
+    if (qpos_init) for (int k = 0; k < o.nq; k++) o.qpos[k] = qpos_init[(size_t)i * o.nq + k];
+    p->rng.push_back(seed * 0x9E3779B97F4A7C15ull + (uint64_t)i * 0xBF58476D1CE4E5B9ull + 1);
+    p->t.push_back(0);
+  }
+  return p;
+}
+void orc_pool_destroy(void* pv) { delete (OrcPool*)pv; }
+int orc_pool_advance(void* pv, int nsteps, int hold, int nthreads) {
+  OrcPool* p = (OrcPool*)pv;
+  if (nthreads < 1) nthreads = 1;
+  std::atomic<int> next(0);
+  const int nworld = (int)p->w.size();
+  auto worker = [&]() {
+    for (;;) {
+      int i = next.fetch_add(1);
+      if (i >= nworld) return;
+      OrcD& o = *p->w[i];
+      for (int k = 0; k < nsteps; k++, p->t[i]++) {
+        if (p->t[i] % hold == 0) for (int a = 0; a < o.nu; a++) o.ctrl[a] = urand(p->rng[i]);
+        o.step();
+      }
+    }
+  };
+  std::vector<std::thread> pool;
+  for (int t = 1; t < nthreads; t++) pool.emplace_back(worker);
+  worker();
+  for (auto& t : pool) t.join();
+  return 0;
+}
+void orc_pool_state(void* pv, double* qpos_out, double* qvel_out) {
+  OrcPool* p = (OrcPool*)pv;
+  for (size_t i = 0; i < p->w.size(); i++) {
+    OrcD& o = *p->w[i];
+    for (int k = 0; k < o.nq; k++) qpos_out[i * o.nq + k] = o.qpos[k];
+    for (int k = 0; k < o.nv; k++) qvel_out[i * o.nv + k] = o.qvel[k];
+  }
 }
 
 }  // extern "C"

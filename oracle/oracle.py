@@ -51,6 +51,11 @@ def lib():
         L.orc_muscle_dynamics.argtypes = [ctypes.c_double, ctypes.c_double, ctypes.c_void_p]
         L.orc_rollout.argtypes = [ctypes.POINTER(_desc.ModelDesc), ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_void_p,
                                   ctypes.c_uint64, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p]
+        L.orc_pool_create.restype = ctypes.c_void_p
+        L.orc_pool_create.argtypes = [ctypes.POINTER(_desc.ModelDesc), ctypes.c_int, ctypes.c_void_p, ctypes.c_uint64]
+        L.orc_pool_destroy.argtypes = [ctypes.c_void_p]
+        L.orc_pool_advance.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_int]
+        L.orc_pool_state.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
         _lib = L
     return _lib
 
@@ -134,3 +139,29 @@ def rollout(model, nworld, nsteps, hold, qpos_init=None, seed=1234, nthreads=1):
     lib().orc_rollout(ctypes.byref(d), nworld, nsteps, hold, qi.ctypes.data if qi is not None else None, seed, nthreads,
                       qo.ctypes.data, vo.ctypes.data)
     return qo, vo
+
+
+class Pool:
+    """`nworld` worlds of one continuing random-ctrl rollout (state, activations and warm start carried across calls): the
+    CPU baseline of bench.py."""
+
+    def __init__(self, model, nworld, qpos_init=None, seed=1234):
+        self._L = lib()
+        self.model, self.nworld = model, nworld
+        self._d, self._keep = _desc.pack(model)
+        qi = np.ascontiguousarray(qpos_init, dtype=np.float64) if qpos_init is not None else None
+        self._h = self._L.orc_pool_create(ctypes.byref(self._d), nworld, qi.ctypes.data if qi is not None else None, seed)
+
+    def advance(self, nsteps, hold, nthreads=1):
+        self._L.orc_pool_advance(self._h, int(nsteps), int(hold), int(nthreads))
+
+    def state(self):
+        q = np.zeros((self.nworld, self.model.nq)); v = np.zeros((self.nworld, self.model.nv))
+        self._L.orc_pool_state(self._h, q.ctypes.data, v.ctypes.data)
+        return q, v
+
+    def __del__(self):
+        try:
+            self._L.orc_pool_destroy(self._h)
+        except Exception:
+            pass

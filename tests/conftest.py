@@ -7,7 +7,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "oracle"))
 
-MODELS = os.path.join(ROOT, "tests", "golden", "models")
+MODELS = os.path.join(ROOT, "myosuite_mjx_b200", "models")
 
 
 def pytest_configure(config):

@@ -1,5 +1,5 @@
 """Compiles the five BASELINE configs' MJCF files (read from the read-only reference checkout) into the
-mjModel-shaped .npz fixtures under tests/golden/models/.  Run in the build container only:
+mjModel-shaped .npz files under myosuite_mjx_b200/models/ (shipped with the package: the GPU box has no /root/reference).  Run in the build container only:
     python tests/golden/make_models.py [/root/reference]
 The GPU box has no /root/reference; tests, smoke() and bench.py load these fixtures instead."""
 import os
@@ -18,7 +18,7 @@ MODELS = {
     "hand_sar": "myosuite/envs/myo/assets/hand/myohand_sar.xml",            # config 4: myoHandReorient8-v0
     "legs": "myosuite/simhive/myo_sim/leg/myolegs.xml",                     # config 5: myoLegWalk-v0
 }
-out = os.path.join(ROOT, "tests", "golden", "models")
+out = os.path.join(ROOT, "myosuite_mjx_b200", "models")
 os.makedirs(out, exist_ok=True)
 for name, rel in MODELS.items():
     m = mjcf.from_xml_path(os.path.join(REF, rel))

@@ -45,7 +45,7 @@ _mod("myosuite.envs.myo.myobase")
 walk_v0 = _load("myosuite.envs.myo.myobase.walk_v0", "myosuite/envs/myo/myobase/walk_v0.py")
 
 from myosuite_mjx_b200 import mjcf   # only for the model's names / masses / keyframes (our own fixture of myolegs.xml)
-mj = mjcf.Model.load(os.path.join(HERE, "models", "legs.npz"))
+mj = mjcf.Model.load(os.path.join(HERE, "..", "..", "myosuite_mjx_b200", "models", "legs.npz"))
 names_b, names_j = [str(x) for x in mj.names_body], [str(x) for x in mj.names_jnt]
 nq, nv, nu, nbody = int(mj.nq), int(mj.nv), int(mj.nu), int(mj.nbody)
 model = SimpleNamespace(body_mass=np.asarray(mj.body_mass, dtype=np.float64), na=int(mj.na), jnt_qposadr=np.asarray(mj.jnt_qposadr),

@@ -24,9 +24,11 @@ def test_reference_arm_line():
     d = json.loads(lines[0])
     assert d["impl"] == "reference" and d["metric"] == "env-steps/s" and d["unit"] == "env-steps/s" and d["higher_is_better"] is True
     assert d["value"] > 0 and d["steps"] == 1 and d["dtype"] == "f64" and d["vs_baseline"] is None
-    assert d["cpu_baseline"]["kind"] == "port" and d["cpu_baseline"]["cores"] >= 1 and d["cpu_baseline"]["value"] == d["value"]
+    assert d["cpu_baseline"]["kind"] in ("port", "mujoco") and d["cpu_baseline"]["cores"] >= 1 and d["cpu_baseline"]["value"] == d["value"]
     assert d["e2e"] == {"value": d["value"], "unit": "env-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
-    assert "8192 worlds/GPU" in d["config"]["workload"]
+    # the workload string names the CPU arm's REAL sample (worlds, steps, threads, which implementation), not the GPU batch
+    assert "CPU arm" in d["config"]["workload"] and "continuing rollout" in d["config"]["workload"] and d["cpu_baseline"]["sample"] in d["config"]["workload"]
+    assert d["parity"].startswith("unpinned")
 
 
 def test_reference_arm_other_ranks_are_silent():
@@ -42,10 +44,14 @@ def test_gpu_arm_line():
               "data", "config", "clocks", "gpu_launches", "e2e", "roofline", "cpu_baseline"):
         assert k in d, k
     assert d["n_gpus"] == 1 and d["steps"] == 20 and d["scaling"] == "weak" and d["dtype"] == "f32" and d["data"] == "synthetic"
-    assert d["gpu_launches"] == 40 and d["config"]["nworld_per_gpu"] == 8192 and d["config"]["fields"] == "all"
+    # 10 kernels per step: kin, tendon, inertia, collide, collideMpr, collideCompact, velact, newton, conout, finish
+    assert d["gpu_launches"] == 200 and d["config"]["nworld_per_gpu"] == 8192 and d["config"]["fields"] == "all"
+    assert d["parity"].startswith("unpinned")
+    ss = d["steady_state"]
+    assert ss["after_steps"] >= 300 and 0 < ss["value"] <= 1.05 * d["value"] and ss["ncon_mean"] > 5, "steady state = the clenched hand"
     r = d["roofline"]
     assert r["bound"] == "hbm" and r["unit"] == "GB/s" and abs(r["frac"] - r["achieved"] / r["peak"]) < 1e-9 and r["traffic"] > 0
     assert abs(r["algorithmic_bytes_per_launch"] - d["config"]["bytes_per_world_step"] * 8192) < 1
     e = d["e2e"]
     assert 0 < e["value"] < d["value"] and e["h2d_bytes_per_step"] > 0 and e["d2h_bytes_per_step"] > 0
-    assert d["cpu_baseline"]["kind"] == "port" and d["cpu_baseline"]["value"] > 0
+    assert d["cpu_baseline"]["kind"] in ("port", "mujoco") and d["cpu_baseline"]["value"] > 0

@@ -3,7 +3,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests")); sys.path.insert(0, os.path.join(ROOT, "oracle"))
 import numpy as np, parity, oracle
 from myosuite_mjx_b200 import mjcf
-m = mjcf.Model.load(os.path.join(ROOT, "tests/golden/models/finger.npz"))
+m = mjcf.Model.load(os.path.join(ROOT, "myosuite_mjx_b200/models/finger.npz"))
 nw = 8
 qpos, qvel, act, ctrl = parity.random_state(m, nw, 1234, qpos_spread=0.9)
 ref, ex = parity.oracle_forward(m, qpos, qvel, act, ctrl, ["ten_length", "ten_J", "site_xpos", "geom_xpos", "geom_xmat"])

@@ -8,7 +8,7 @@ from myosuite_mjx_b200 import mjcf
 
 names = sys.argv[1:] or ["elbow", "hand", "hand_pose", "hand_sar", "legs", "finger"]
 for name in names:
-    m = mjcf.Model.load(os.path.join(ROOT, "tests/golden/models", name + ".npz"))
+    m = mjcf.Model.load(os.path.join(ROOT, "myosuite_mjx_b200/models", name + ".npz"))
     nw = 48
     qpos, qvel, act, ctrl = parity.random_state(m, nw, 1234, qpos_spread=0.9)
     t = time.time()

@@ -6,7 +6,7 @@ import numpy as np
 import parity, oracle
 from myosuite_mjx_b200 import mjcf
 name = sys.argv[1] if len(sys.argv) > 1 else "hand_sar"
-m = mjcf.Model.load(os.path.join(ROOT, "tests/golden/models", name + ".npz"))
+m = mjcf.Model.load(os.path.join(ROOT, "myosuite_mjx_b200/models", name + ".npz"))
 nw = 32
 qpos, qvel, act, ctrl = parity.random_state(m, nw, 1234, qpos_spread=0.9)
 F = ["qacc", "qacc_smooth", "qfrc_constraint", "qfrc_smooth"]

@@ -6,7 +6,7 @@ import numpy as np
 import parity
 from myosuite_mjx_b200 import mjcf
 for name in sys.argv[1:] or ["finger", "hand", "legs", "hand_sar", "elbow"]:
-    m = mjcf.Model.load(os.path.join(ROOT, "tests/golden/models", name + ".npz"))
+    m = mjcf.Model.load(os.path.join(ROOT, "myosuite_mjx_b200/models", name + ".npz"))
     nw = 32
     qpos, qvel, act, ctrl = parity.random_state(m, nw, 1234, qpos_spread=0.9)
     ref, ex = parity.oracle_forward(m, qpos, qvel, act, ctrl, ["ten_length"])
