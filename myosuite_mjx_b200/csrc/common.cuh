@@ -142,6 +142,11 @@ struct Tm { int tl, nw; };
 #define TFOR_PRAGMA_(x) _Pragma(#x)
 #define TFOR_PRAGMA(n) TFOR_PRAGMA_(unroll n)
 #define TFOR(i, n) TFOR_PRAGMA(TFOR_UNROLL) for (int i = t.tl; i < (n); i += TEAM)
+// the warps are bound by the latency of dependent loads: the hot inner loops are unrolled so that several loads are in flight
+#ifndef HOT_UNROLL
+#define HOT_UNROLL 2   // 1: +4 % step time, 4: same, 8: +1.3 % (profiles/r2_warps_per_tile.txt)
+#endif
+#define HOT TFOR_PRAGMA(HOT_UNROLL)
 
 
 // frame record in the per-world scratch: pos[3], quat[4], mat[9]
@@ -1248,6 +1253,7 @@ __device__ __noinline__ void baseMul(int slot, SP sm, Tm t, int ncon, SP x, SP o
     auto J0 = sm + L.conJ + b * nv; auto J1 = sm + L.conJ + min(b2, nbr - 1) * nv;
     float a0 = 0.f, a1 = 0.f, c0 = 0.f, c1 = 0.f;
     int k = 0;
+    HOT
     for (; k + 1 < nv; k += 2) {
       const float x0 = x[k], x1 = x[k + 1];
       a0 = fmaf(J0[k], x0, a0); a1 = fmaf(J0[k + 1], x1, a1); c0 = fmaf(J1[k], x0, c0); c1 = fmaf(J1[k + 1], x1, c1);
@@ -1277,7 +1283,9 @@ __device__ __noinline__ void mulMsparse(int slot, SP qM, SP x, SP out, Tm t) {
   TFOR(i, D.nv) {
     const int a = D.dof_Madr[i], d = D.dof_rowlen[i];
     float acc = 0.f;
+    HOT
     for (int q = 0; q < d; q++) acc = fmaf(qM[a + q], x[D.M_col[a + q]], acc);
+    HOT
     for (int e = D.desc_start[i]; e < D.desc_start[i + 1]; e++) acc = fmaf(qM[D.desc_idx[e]], x[D.desc_dof[e]], acc);
     out[i] = acc;
   }
@@ -1350,6 +1358,7 @@ __device__ __noinline__ void constraintForce(int slot, SP sm, Tm t, int ncon, in
     auto Jk = sm + L.conJ;
     float a0 = 0.f, a1 = 0.f, a2 = 0.f, e0 = 0.f, e1 = 0.f, e2 = 0.f;
     int b = 0;
+    HOT
     for (; b + 1 < nbr; b += 2) {
       const float f0 = bf[b], f1 = bf[b + 1];
       auto Ja = Jk + b * nv; auto Jb = Jk + (b + 1) * nv;

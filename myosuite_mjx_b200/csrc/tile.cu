@@ -554,11 +554,13 @@ __device__ __noinline__ void hessianAssemble(int slot, SP sm, Tm t, SP H, int nc
       const float Wnn = Wi[0], Wnt0 = Wi[1], Wnt1 = Wi[2], Wnt2 = Wi[3], Wtt0 = Wi[4], Wtt1 = Wi[5], Wtt2 = Wi[6];
       auto J = sm + L.conJ + (c * nb) * nv; auto Uo = sm + L.conU + (c * nb) * nv;
       if (nb == 3) {
+        HOT
         for (int k = 0; k < nv; k++) {
           const float jn = J[k], j1 = J[nv + k], j2 = J[2 * nv + k];
           Uo[k] = fmaf(Wnt1, j2, fmaf(Wnt0, j1, Wnn * jn)); Uo[nv + k] = fmaf(Wnt0, jn, Wtt0 * j1); Uo[2 * nv + k] = fmaf(Wnt1, jn, Wtt1 * j2);
         }
       } else if (nb == 4) {
+        HOT
         for (int k = 0; k < nv; k++) {
           const float jn = J[k], j1 = J[nv + k], j2 = J[2 * nv + k], j3 = J[3 * nv + k];
           Uo[k] = fmaf(Wnt2, j3, fmaf(Wnt1, j2, fmaf(Wnt0, j1, Wnn * jn)));
@@ -667,6 +669,7 @@ __device__ __noinline__ void choleskyTile(int nv, SP H, SP Hd, Tm t) {
       auto Hr = H + TRI(r); auto Hj = H + TRI(j);
       float s0 = Hr[j], s1 = 0.f;
       int k = 0;
+      HOT
       for (; k + 1 < j; k += 2) { s0 = fmaf(-Hr[k], Hj[k], s0); s1 = fmaf(-Hr[k + 1], Hj[k + 1], s1); }
       if (k < j) s0 = fmaf(-Hr[k], Hj[k], s0);
       Hr[j] = s0 + s1;
@@ -703,6 +706,7 @@ template <int K> __device__ __forceinline__ void lsEvalTile(int slot, SP sm, Tm 
 #pragma unroll
   for (int i = 0; i < 4 * K; i++) q[i] = 0.f;
   const int neq = D.neq;
+  TFOR_PRAGMA(2)
   for (int r = t.tl; r < nefc; r += t.nw) {
     const float jar = EFC(E_JAR, r), jv = EFC(E_JV, r), Dr = EFC(E_D, r);
 #pragma unroll
