@@ -401,6 +401,7 @@ __device__ __forceinline__ bool segIntersect(const float* p1, const float* p2, c
   if (fabsf(det) < MINVAL) return false;
   const float a = ((p4[0] - p3[0]) * (p1[1] - p3[1]) - (p4[1] - p3[1]) * (p1[0] - p3[0])) / det;
   const float b = ((p2[0] - p1[0]) * (p1[1] - p3[1]) - (p2[1] - p1[1]) * (p1[0] - p3[0])) / det;
+  if (a > 1.f - 1e-4f && b > 1.f - 1e-4f) return false;   // the parts only meet at their end points (grazing path): not a crossing, see oracle/mjstep_oracle.cpp
   return a >= 0.f && a <= 1.f && b >= 0.f && b <= 1.f;
 }
 __device__ __noinline__ float wrapCircle(float* pnt, const float* d, const float* sd, float rad) {
@@ -410,7 +411,10 @@ __device__ __noinline__ float wrapCircle(float* pnt, const float* d, const float
   float a = -(dx * d[0] + dy * d[1]) / fmaxf(MINVAL, dd);
   a = clipf(a, 0.f, 1.f);
   const float nx = d[0] + a * dx, ny = d[1] + a * dy;
-  if (nx * nx + ny * ny > sqr && (!sd || sd[0] * nx + sd[1] * ny >= 0.f)) return -1.f;
+  // side-site rule with a tie band (oracle/mjstep_oracle.cpp wrapCircle has the reasoning): within 1e-5 of the product's scale
+  // the side site counts as "same side", so float32 and float64 take the same branch at joint-limit poses
+  const float nn = nx * nx + ny * ny;
+  if (nn > sqr && (!sd || sd[0] * nx + sd[1] * ny >= -1e-5f * rad * sqrtf(nn))) return -1.f;
   if (sq0 < sqr || sq1 < sqr) return -1.f;
   const float s0 = sqrtf(sq0 - sqr), s1 = sqrtf(sq1 - sqr);
   float sol[2][4], good[2];

@@ -968,9 +968,9 @@ class _Compiler:
                 kv.append(_floats(k.attrib["qvel"], m.nv) if "qvel" in k.attrib else np.zeros(m.nv))
                 ka.append(_floats(k.attrib["act"], m.na) if "act" in k.attrib else np.zeros(m.na))
         m.nkey = len(kq)
-        m.key_qpos = np.array(kq).reshape(-1, m.nq)
-        m.key_qvel = np.array(kv).reshape(-1, m.nv)
-        m.key_act = np.array(ka).reshape(-1, m.na)
+        m.key_qpos = np.array(kq, dtype=np.float64).reshape(len(kq), m.nq)
+        m.key_qvel = np.array(kv, dtype=np.float64).reshape(len(kq), m.nv)
+        m.key_act = np.array(ka, dtype=np.float64).reshape(len(kq), m.na)
         touch = []
         for sec in self.root.findall("sensor"):
             for s in sec:

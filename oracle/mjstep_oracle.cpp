@@ -127,11 +127,17 @@ template <typename T> inline void crossForce(T* r, const T* vel, const T* f) {
 
 // ------------------------------------------------------------------------------------------ tendon wrapping
 // 2-D helpers of mju_wrap (MuJoCo docs, "Tendon wrapping")
+// Do the straight parts site0 -> tangent0 and site1 -> tangent1 cross?  MuJoCo tests the closed parameter square [0,1]^2.
+// When the straight path grazes the circle the two tangent points coincide and the parts meet exactly at their END points
+// (a = b = 1): whether that counts as a crossing is then rounding noise, and it flips the wrap between a zero arc and the
+// long way round (2 cm of tendon length on the finger at its joint limits, differently in float32 and float64).  A meeting
+// within 1e-4 of both end points is therefore not a crossing -- the same branch in every precision.
 template <typename T> bool segIntersect(const T* p1, const T* p2, const T* p3, const T* p4) {
   T det = (p4[1] - p3[1]) * (p2[0] - p1[0]) - (p4[0] - p3[0]) * (p2[1] - p1[1]);
   if (std::fabs(det) < T(kMinVal)) return false;
   T a = ((p4[0] - p3[0]) * (p1[1] - p3[1]) - (p4[1] - p3[1]) * (p1[0] - p3[0])) / det;
   T b = ((p2[0] - p1[0]) * (p1[1] - p3[1]) - (p2[1] - p1[1]) * (p1[0] - p3[0])) / det;
+  if (a > T(1) - T(1e-4) && b > T(1) - T(1e-4)) return false;
   return a >= 0 && a <= 1 && b >= 0 && b <= 1;
 }
 template <typename T> T arcAngle(const T* p0, const T* p1, int ind) {
@@ -154,7 +160,12 @@ template <typename T> T wrapCircle(T* pnt, const T* d, const T* sd, T rad) {
   T a = -(dif[0] * d[0] + dif[1] * d[1]) / std::max(T(kMinVal), dd);
   a = clip(a, T(0), T(1));
   T near[2] = {d[0] + a * dif[0], d[1] + a * dif[1]};
-  if (near[0] * near[0] + near[1] * near[1] > sqr && (!sd || sd[0] * near[0] + sd[1] * near[1] >= 0)) return -1;
+  // Side-site rule: a straight segment that clears the circle still wraps when it passes on the far side of the side site.
+  // At a pose where the side site lies exactly on the segment's normal (the finger at its joint limits: qpos = 0) the sign
+  // of this dot product is rounding noise and flips a wrap of ~2 cm on or off, differently in float32 and float64.  Ties
+  // within 1e-5 of the product's scale (|sd| = rad) count as "same side": the same branch in every precision.
+  const T nn = near[0] * near[0] + near[1] * near[1];
+  if (nn > sqr && (!sd || sd[0] * near[0] + sd[1] * near[1] >= T(-1e-5) * rad * std::sqrt(nn))) return -1;
   if (sq0 < sqr || sq1 < sqr) return -1;
   T s0 = std::sqrt(sq0 - sqr), s1 = std::sqrt(sq1 - sqr);
   T sol[2][4], good[2];

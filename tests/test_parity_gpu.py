@@ -44,6 +44,28 @@ def test_forward_stage_fields(fwd, name):
     assert not bad, f"{name}: fields beyond rel 1e-4: {bad}"
 
 
+def test_finger_wrap_ties_at_joint_limits(models):
+    """Config 2 (myoFingerPoseRandom-v0): with the two distal joints exactly on their limit (qpos = 0, also the model's qpos0)
+    site 11 lies on the tangent from site 5 to wrap cylinder 4: the straight path grazes the cylinder, the two tangent points
+    coincide, and MuJoCo's crossing test of the two straight parts is decided by rounding -- a zero arc or the long way round,
+    2 cm of tendon length (profiles/r1w_parity.txt: ten_J off by 0.64 in 2 of 48 worlds in round 1).  wrapCircle's tie rules
+    (oracle/mjstep_oracle.cpp segIntersect, wrapCircle) give float32 and float64 the same branch: 48 worlds at spread 0.9
+    (worlds 8 and 13 are such poses) and 32 worlds pinned to the limit agree with the float64 oracle to 1e-4."""
+    m = models("finger")
+    fields = ["ten_length", "ten_J", "ten_velocity", "actuator_length", "actuator_moment", "qfrc_actuator", "qacc_smooth"]
+    for nw, pin in ((48, False), (32, True)):
+        qpos, qvel, act, ctrl = parity.random_state(m, nw, 1234, qpos_spread=0.9)
+        if pin:
+            qpos[:, 2:] = 0.0
+        else:
+            assert (qpos[[8, 13], 2:] == 0.0).all(), "the regression worlds moved: regenerate"
+        ref, ex = parity.oracle_forward(m, qpos, qvel, act, ctrl, fields)
+        model, d, got = parity.gpu_forward(m, qpos, qvel, act, ctrl, nconmax=32, njmax=160)
+        rep = parity.field_errors(ref, got, fields)
+        bad = {k: v for k, v in rep.items() if v[1] > 1e-4}
+        assert not bad, f"finger, pinned={pin}: fields beyond rel 1e-4: {bad}"
+
+
 @pytest.mark.parametrize("name", MODELS)
 def test_contact_and_row_indices_exact(fwd, name):
     m, ref, ex, got, d = fwd(name)
