@@ -5,6 +5,9 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <algorithm>
+#include <atomic>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -13,9 +16,11 @@
 
 
 namespace {
-int64_t g_launches = 0;
+std::atomic<int64_t> g_launches{0};
 thread_local std::string g_err;
-bool g_slot_used[64] = {false};
+bool g_slot_used[64] = {false};   // guarded by g_slot_mutex: batches may be created and destroyed from several host threads
+std::mutex g_slot_mutex;
+void releaseSlot(int slot) { if (slot >= 0) { std::lock_guard<std::mutex> lk(g_slot_mutex); g_slot_used[slot] = false; } }
 int fail(int code, const std::string& msg) { g_err = msg; return code; }
 }  // namespace
 int myo_fail(int code, const std::string& msg) { return fail(code, msg); }
@@ -128,18 +133,21 @@ int myo_batch_create(const myo_model* m, int nworld, int nconmax, int njmax, myo
   if (cudaSetDevice(m->device) != cudaSuccess) return fail(MYO_ERR_CUDA, "cudaSetDevice failed");
   myo_batch* b = new myo_batch();
   b->model = m; b->D = m->D; b->nworld = nworld; b->slot = -1; b->dirty = true;
-  for (int i = 0; i < MYO_PARAM_SLOTS; i++) if (!g_slot_used[i]) { b->slot = i; g_slot_used[i] = true; break; }
-  if (b->slot < 0) { delete b; return fail(MYO_ERR_ARG, "too many live batches (8 constant-memory parameter slots)"); }
+  {
+    std::lock_guard<std::mutex> lk(g_slot_mutex);
+    for (int i = 0; i < MYO_PARAM_SLOTS; i++) if (!g_slot_used[i]) { b->slot = i; g_slot_used[i] = true; break; }
+  }
+  if (b->slot < 0) { delete b; return fail(MYO_ERR_ARG, "too many live batches (16 constant-memory parameter slots)"); }
   memset(&b->F, 0, sizeof(b->F));
   try {
     myo_make_layout(b->D, nconmax, njmax, b->L);
-  } catch (const std::string& e) { g_slot_used[b->slot] = false; delete b; return fail(MYO_ERR_ARG, e); }
+  } catch (const std::string& e) { releaseSlot(b->slot); delete b; return fail(MYO_ERR_ARG, e); }
   {
     void* p = nullptr;
     // tile-blocked scratch [tiles][L.total][32]; zeroed once: a record the kernels have not written yet (rows past an
     // overflow, lanes of a partial tile) reads as zeros
     const size_t bytes = (size_t)((nworld + 31) / 32) * b->L.total * 32 * sizeof(float);
-    if (cudaMalloc(&p, bytes) != cudaSuccess || cudaMemset(p, 0, bytes) != cudaSuccess) { g_slot_used[b->slot] = false; delete b; return fail(MYO_ERR_CUDA, "cudaMalloc of the per-world scratch failed"); }
+    if (cudaMalloc(&p, bytes) != cudaSuccess || cudaMemset(p, 0, bytes) != cudaSuccess) { releaseSlot(b->slot); delete b; return fail(MYO_ERR_CUDA, "cudaMalloc of the per-world scratch failed"); }
     b->owned.push_back(p); b->scratch = (float*)p;
     // work list of the convex narrow phase: at most every MPR-type candidate pair of every world
     b->X.mpr_cap = (int)std::min<int64_t>((int64_t)nworld * std::max(1, b->D.nmprpair), (int64_t)1 << 30);
@@ -163,7 +171,7 @@ void myo_batch_destroy(myo_batch* b) {
   for (void* p : b->owned) cudaFree(p);
   for (int i = 0; i < 2; i++) if (b->side[i]) { cudaStreamSynchronize((cudaStream_t)b->side[i]); cudaStreamDestroy((cudaStream_t)b->side[i]); }
   for (int i = 0; i < 6; i++) if (b->ev[i]) cudaEventDestroy((cudaEvent_t)b->ev[i]);
-  if (b->slot >= 0) g_slot_used[b->slot] = false;
+  releaseSlot(b->slot);
   delete b;
 }
 int myo_batch_nconmax(const myo_batch* b) { return b ? b->D.nconmax : 0; }

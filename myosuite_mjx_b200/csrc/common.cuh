@@ -28,7 +28,8 @@
 #endif
 #define TEAM (t.nw)   // item stride of a loop = the NW warps of the tile's CTA (NW = blockDim.x / 32, a launch parameter)
 struct TParams { DevModel D; SmemLayout L; FieldPtrs F; TileAux X; };
-#define MYO_NSLOT 8
+#define MYO_NSLOT MYO_PARAM_SLOTS
+static_assert(sizeof(TParams) * (MYO_NSLOT + 1) <= 60 * 1024, "parameter slots exceed constant memory");
 __constant__ TParams tP[MYO_NSLOT + 1];   // slot MYO_NSLOT stays zero: "materialise nothing" (inner substeps)
 namespace {
 

@@ -11,8 +11,8 @@ Field names are mjData's; every `Data` attribute is a torch CUDA tensor of logic
 leading axis) that the kernel reads and writes in place.  PHYSICAL layout is struct-of-arrays with the world axis
 fastest (`storage[k, world]`; the attribute is the transposed, strided view), which is what makes every warp access
 one coalesced line.  Zero-copy: the storage is bound to the batch through `myo_batch_bind`; any DLPack producer of a
-`[k, nworld]` buffer can be bound the same way, see `Data.bind`.  `step` returns the same `Data` object; call
-`data.clone()` first if the functional, non-aliasing behaviour of `mjx.step` is needed.
+`[k, nworld]` buffer can be bound the same way, see `Data.bind`.  `step` steps in place by default (a donated
+argument); `step(model, data, donate=False)` is the functional, non-aliasing `mjx.step` (two ping-ponged buffer sets).
 Unsupported model features raise `NotImplementedError` at `put_model`, as MJX does.  No CPU fallback exists.
 """
 from __future__ import annotations
@@ -83,6 +83,9 @@ class Data:
         self.ctas_per_sm = L.myo_batch_ctas_per_sm(h)
         self.engine = "phase" if L.myo_batch_engine(h) == 1 else "mono"
         self._t = {}
+        # several Data objects can share one batch handle (the two buffer sets of the functional step): `bound` is the one
+        # whose buffers the library currently writes, `refs` counts the sharers
+        self._share = {"bound": self, "refs": 1}
         dev = torch.device("cuda", model.device)
         if fields == "all":
             names = [n.lower() for n in _desc.FIELD_NAMES if n.lower() not in INPUT_FIELDS]
@@ -108,8 +111,30 @@ class Data:
         if not tensor.is_cuda or not tensor.is_contiguous():
             raise ValueError("bound buffers must be contiguous [k, nworld] CUDA tensors")
         fid = _desc.FIELD_ID[name.lower()]
-        _lib.check(_lib.lib().myo_batch_bind(self._h, fid, ctypes.c_void_p(tensor.data_ptr()), tensor.numel() * tensor.element_size()))
         self._t[name.lower()] = tensor
+        if self._share["bound"] is self:
+            _lib.check(_lib.lib().myo_batch_bind(self._h, fid, ctypes.c_void_p(tensor.data_ptr()), tensor.numel() * tensor.element_size()))
+
+    def _ensure_bound(self):
+        """make this object's buffers the ones the library reads and writes (no-op unless a partner set is bound)"""
+        if self._share["bound"] is not self:
+            L = _lib.lib()
+            for k, t in self._t.items():
+                _lib.check(L.myo_batch_bind(self._h, _desc.FIELD_ID[k], ctypes.c_void_p(t.data_ptr()), t.numel() * t.element_size()))
+            self._share["bound"] = self
+
+    def _partner(self):
+        """the other buffer set of the ping-pong (allocated on first use): same batch, same fields, its own tensors"""
+        p = self.__dict__.get("_pong")
+        if p is None:
+            p = Data.__new__(Data)
+            for k in ("model", "nworld", "_h", "nconmax", "njmax", "smem_bytes", "team", "ctas_per_sm", "engine", "_share"):
+                p.__dict__[k] = self.__dict__[k]
+            p.__dict__["_t"] = {k: torch.zeros_like(v) for k, v in self._t.items()}
+            p.__dict__["_pong"] = self
+            self.__dict__["_pong"] = p
+            self._share["refs"] += 1
+        return p
 
     def set_pipelined(self, on=True):
         """Opt in to pipelined wide outputs (include/myostep.h, myo_batch_set_pipelined): the wide-output kernel of a step
@@ -159,6 +184,7 @@ class Data:
         h = ctypes.c_void_p()
         _lib.check(L.myo_batch_create(self.model._h, self.nworld, self.nconmax, self.njmax, ctypes.byref(h)))
         d._h, d.nconmax, d.njmax, d._t = h, self.nconmax, self.njmax, {}
+        d.__dict__["_share"] = {"bound": d, "refs": 1}
         d.smem_bytes, d.team, d.ctas_per_sm = self.smem_bytes, L.myo_batch_team(h), 1
         d.engine = "phase" if L.myo_batch_engine(h) == 1 else "mono"
         if self.__dict__.get("_pipelined"):
@@ -169,7 +195,9 @@ class Data:
 
     def __del__(self):
         try:
-            _lib.lib().myo_batch_destroy(self._h)
+            self._share["refs"] -= 1
+            if self._share["refs"] <= 0:
+                _lib.lib().myo_batch_destroy(self._h)
         except Exception:
             pass
 
@@ -219,6 +247,7 @@ def _mask_ptr(data, mask):
 def forward(model, data, mask=None) -> Data:
     """mjx.forward / mj_forward (reference: sim.forward(), myosuite/robot/robot.py:979); `mask` restricts it to the
     flagged worlds."""
+    data._ensure_bound()
     p, keep = _mask_ptr(data, mask)
     _lib.check(_lib.lib().myo_forward_masked(data._h, p, _stream()) if mask is not None else _lib.lib().myo_forward(data._h, _stream()))
     return data
@@ -228,20 +257,37 @@ def refresh(model, data, mask=None) -> Data:
     """mj_step1-style refresh of the position- and velocity-dependent fields from the current state (what dm_control's
     Physics.step leaves behind on the classic path, reference: myosuite/physics/mj_sim_scene.py:55); contacts, forces,
     accelerations and the warm start are left as the last full pass wrote them."""
+    data._ensure_bound()
     p, keep = _mask_ptr(data, mask)
     _lib.check(_lib.lib().myo_forward_posvel(data._h, p, _stream()))
     return data
 
 
-def step(model, data, nsubsteps=1) -> Data:
+def step(model, data, nsubsteps=1, donate=True) -> Data:
     """mjx.step (reference: myosuite/mjx/play.py:47); `nsubsteps` fuses n mj_steps with ctrl held
-    (reference: sim.advance(substeps=n_frames), myosuite/robot/robot.py:880-882)."""
-    _lib.check(_lib.lib().myo_step(data._h, int(nsubsteps), _stream()))
-    return data
+    (reference: sim.advance(substeps=n_frames), myosuite/robot/robot.py:880-882).
+
+    `donate=True` (default, the fast path): the batch is stepped in place and the same `Data` is returned -- what
+    `jax.jit(mjx.step, donate_argnums=1)` does.  `donate=False` gives mjx.step's functional contract: `data` keeps the old
+    state and every old field, the result is ANOTHER `Data` (reference: myodm_v0.py:278-287 reads pipeline_state0 after
+    pipeline_step).  The two objects share one batch and ping-pong between two buffer sets (SURVEY.md 8b "Ownership"), so the
+    result of step k reuses the buffers of step k-2: keep at most the last two states alive, or `clone()`."""
+    if donate:
+        data._ensure_bound()
+        _lib.check(_lib.lib().myo_step(data._h, int(nsubsteps), _stream()))
+        return data
+    new = data._partner()
+    for k in STATE_FIELDS + INPUT_FIELDS:
+        if k in data._t:
+            new._t[k].copy_(data._t[k])
+    new._ensure_bound()
+    _lib.check(_lib.lib().myo_step(new._h, int(nsubsteps), _stream()))
+    return new
 
 
 def reset(model, data, mask=None) -> Data:
     """mj_resetData + mj_forward on the masked worlds (reference: myosuite/robot/robot.py:976-979)."""
+    data._ensure_bound()
     if mask is not None:
         mask = mask.to(device=data.qpos.device, dtype=torch.int32).reshape(-1).contiguous()
     _lib.check(_lib.lib().myo_reset(data._h, ctypes.c_void_p(mask.data_ptr()) if mask is not None else None, _stream()))

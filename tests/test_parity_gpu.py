@@ -341,6 +341,40 @@ def test_deterministic_and_output_mask_invariant(models):
         assert torch.equal(outs[0][k], outs[1][k]) and torch.equal(outs[0][k], outs[2][k])
 
 
+def test_functional_step_keeps_the_old_state(models):
+    """mjx.step's functional contract (reference: myodm_v0.py:278-287 reads pipeline_state0 after pipeline_step):
+    step(model, data, donate=False) leaves every field of `data` untouched and returns another Data with the stepped state,
+    bit-identical to an in-place step; the two ping-pong, so the result of step k reuses the buffers of step k-2.  No extra
+    batch (constant-memory slot) is taken, and 12 batches can be alive at once."""
+    import torch
+    from myosuite_mjx_b200 import mjx
+    m = models("hand")
+    nw = 64
+    qpos, qvel, act, ctrl = parity.random_state(m, nw, 3, qpos_spread=0.5)
+    model = mjx.put_model(m)
+    a = mjx.put_data(model, dict(qpos=qpos, qvel=qvel, act=act, ctrl=ctrl), nworld=nw, fields="all")
+    b = mjx.put_data(model, dict(qpos=qpos, qvel=qvel, act=act, ctrl=ctrl), nworld=nw, fields="all")
+    mjx.forward(model, a)
+    before = {f: getattr(a, f).clone() for f in a.fields()}
+    a1 = mjx.step(model, a, 2, donate=False)
+    mjx.step(model, b, 2)
+    torch.cuda.synchronize()
+    assert a1 is not a and a1._h is a._h
+    for f, v in before.items():
+        assert torch.equal(getattr(a, f), v), f"{f}: the functional step changed its input"
+    for f in ("qpos", "qvel", "act", "time", "qacc_warmstart", "site_xpos", "efc_force", "ncon"):
+        assert torch.equal(getattr(a1, f), getattr(b, f)), f"{f}: functional step differs from the in-place step"
+    assert float(a1.time[0, 0]) > float(a.time[0, 0])                   # myodm_v0.py:279 reads the old time after the step
+    a2 = mjx.step(model, a1, 1, donate=False)
+    mjx.step(model, b, 1)
+    torch.cuda.synchronize()
+    assert a2 is a and torch.equal(a2.qpos, b.qpos)                     # ping-pong: two buffer sets
+    mjx.forward(model, a1)                                              # either object can be used again: it rebinds itself
+    torch.cuda.synchronize()
+    extra = [mjx.make_data(model, 8, "core") for _ in range(10)]        # 12 live batches
+    assert len(extra) == 10
+
+
 def test_reset_and_masked_reset(models):
     import torch
     from myosuite_mjx_b200 import mjx
