@@ -354,7 +354,7 @@ def test_functional_step_keeps_the_old_state(models):
     model = mjx.put_model(m)
     a = mjx.put_data(model, dict(qpos=qpos, qvel=qvel, act=act, ctrl=ctrl), nworld=nw, fields="all")
     b = mjx.put_data(model, dict(qpos=qpos, qvel=qvel, act=act, ctrl=ctrl), nworld=nw, fields="all")
-    mjx.forward(model, a)
+    mjx.forward(model, a); mjx.forward(model, b)      # (a forward pass leaves its qacc as the next warm start)
     before = {f: getattr(a, f).clone() for f in a.fields()}
     a1 = mjx.step(model, a, 2, donate=False)
     mjx.step(model, b, 2)
