@@ -175,6 +175,15 @@ typedef enum myo_field {
   MYO_F_QFRC_APPLIED,    /* [nv]   optional input (mjData.qfrc_applied): added to qfrc_smooth when bound */
   MYO_F_SENSORDATA,      /* [nsensor] touch sensors (mj_sensorAcc): summed normal force of the contacts of the site's body whose
                             normal ray meets the site's volume */
+  /* Optional per-world MODEL overrides (inputs).  The compiled model is one immutable table set shared by every world; these
+   * cover what the reference's envs rewrite in mjModel per episode: the manipulated object's shape
+   * (myosuite/envs/myo/myobase/reorient_sar_v0.py:207-245: geom_type, geom_size, geom_pos) and muscle weakness
+   * (myosuite/envs/myo/base_v0.py:64-68: actuator_gainprm[:, 2]).  An unbound field, or an entry holding its "keep" value,
+   * means the compiled model's value. */
+  MYO_F_GEOM_TYPE_OVR,   /* [ngeom] int32 mjtGeom of a collision geom (sphere 2, capsule 3, ellipsoid 4, cylinder 5, box 6); < 0 = keep */
+  MYO_F_GEOM_SIZE_OVR,   /* [ngeom,3] geom_size; size[0] <= 0 = keep */
+  MYO_F_GEOM_POS_OVR,    /* [ngeom,3] geom_pos in its body's frame; NaN in x = keep */
+  MYO_F_ACT_GAINSCALE,   /* [nu] factor on the gain of each actuator (a muscle's peak force); bound buffers start at 1 */
   MYO_F_COUNT
 } myo_field;
 

@@ -35,12 +35,14 @@ const char* kFieldNames[MYO_F_COUNT] = {
     "qfrc_passive", "qfrc_spring", "qfrc_damper", "qfrc_actuator", "qfrc_smooth", "qfrc_constraint", "qfrc_inverse", "ncon",
     "nefc", "contact_geom", "contact_dim", "contact_efc_address", "contact_dist", "contact_pos", "contact_frame",
     "contact_includemargin", "contact_friction", "contact_solref", "contact_solimp", "efc_J", "efc_pos", "efc_margin", "efc_D",
-    "efc_aref", "efc_force", "efc_type", "solver_niter", "status", "qfrc_applied", "sensordata"};
+    "efc_aref", "efc_force", "efc_type", "solver_niter", "status", "qfrc_applied", "sensordata", "geom_type_ovr", "geom_size_ovr",
+    "geom_pos_ovr", "act_gainscale"};
 
 bool isIntField(int f) {
   switch (f) {
     case MYO_F_TEN_WRAPADR: case MYO_F_TEN_WRAPNUM: case MYO_F_WRAP_OBJ: case MYO_F_NCON: case MYO_F_NEFC: case MYO_F_CONTACT_GEOM:
-    case MYO_F_CONTACT_DIM: case MYO_F_CONTACT_EFC_ADDRESS: case MYO_F_EFC_TYPE: case MYO_F_SOLVER_NITER: case MYO_F_STATUS: return true;
+    case MYO_F_CONTACT_DIM: case MYO_F_CONTACT_EFC_ADDRESS: case MYO_F_EFC_TYPE: case MYO_F_SOLVER_NITER: case MYO_F_STATUS:
+    case MYO_F_GEOM_TYPE_OVR: return true;
     default: return false;
   }
 }
@@ -52,7 +54,9 @@ int64_t fieldCount(const DevModel& D, int f) {
     case MYO_F_QFRC_PASSIVE: case MYO_F_QFRC_SPRING: case MYO_F_QFRC_DAMPER: case MYO_F_QFRC_ACTUATOR: case MYO_F_QFRC_SMOOTH:
     case MYO_F_QFRC_CONSTRAINT: case MYO_F_QFRC_INVERSE: case MYO_F_QFRC_APPLIED: return nv;
     case MYO_F_ACT: case MYO_F_ACT_DOT: return D.na;
-    case MYO_F_CTRL: case MYO_F_ACTUATOR_LENGTH: case MYO_F_ACTUATOR_VELOCITY: case MYO_F_ACTUATOR_FORCE: return D.nu;
+    case MYO_F_CTRL: case MYO_F_ACTUATOR_LENGTH: case MYO_F_ACTUATOR_VELOCITY: case MYO_F_ACTUATOR_FORCE: case MYO_F_ACT_GAINSCALE: return D.nu;
+    case MYO_F_GEOM_TYPE_OVR: return D.ngeom;
+    case MYO_F_GEOM_SIZE_OVR: case MYO_F_GEOM_POS_OVR: return 3 * (int64_t)D.ngeom;
     case MYO_F_SENSORDATA: return D.nsensor;
     case MYO_F_TIME: case MYO_F_NCON: case MYO_F_NEFC: case MYO_F_SOLVER_NITER: case MYO_F_STATUS: return 1;
     case MYO_F_XPOS: case MYO_F_XIPOS: case MYO_F_SUBTREE_COM: return 3 * nb;
@@ -150,7 +154,7 @@ int myo_batch_create(const myo_model* m, int nworld, int nconmax, int njmax, myo
     if (cudaMalloc(&p, bytes) != cudaSuccess || cudaMemset(p, 0, bytes) != cudaSuccess) { releaseSlot(b->slot); delete b; return fail(MYO_ERR_CUDA, "cudaMalloc of the per-world scratch failed"); }
     b->owned.push_back(p); b->scratch = (float*)p;
     // work list of the convex narrow phase: at most every MPR-type candidate pair of every world
-    b->X.mpr_cap = (int)std::min<int64_t>((int64_t)nworld * std::max(1, b->D.nmprpair), (int64_t)1 << 30);
+    b->X.mpr_cap = (int)std::min<int64_t>((int64_t)nworld * std::max(1, b->D.npair), (int64_t)1 << 30);   // (a type override can turn any pair convex)
     void* q = nullptr;
     if (cudaMalloc(&q, (size_t)b->X.mpr_cap * sizeof(int2) + 256) != cudaSuccess || cudaMemset(q, 0, 256) != cudaSuccess) { myo_batch_destroy(b); return fail(MYO_ERR_CUDA, "cudaMalloc of the narrow-phase work list failed"); }
     b->owned.push_back(q); b->X.mpr_count = (int*)q; b->X.mpr_list = (int2*)((char*)q + 256);
@@ -252,10 +256,10 @@ static int launchPhases(myo_batch* b, int nsub, int forward_only, const int32_t*
   // mj_collision = broad phase + closed-form pairs, the listed convex pairs one per lane, ordered compaction
   auto collide = [&](int fslot) {
     bool r = true;
-    if (b->D.npair > 0 && b->D.nmprpair > 0) r &= cudaMemsetAsync(b->X.mpr_count, 0, sizeof(int), (cudaStream_t)cur) == cudaSuccess;
+    if (b->D.npair > 0) r &= cudaMemsetAsync(b->X.mpr_count, 0, sizeof(int), (cudaStream_t)cur) == cudaSuccess;
     r &= tile(MYO_K_COLLIDE, fslot, 0) == 0;
     if (b->D.npair > 0) {
-      if (b->D.nmprpair > 0) r &= tile(MYO_K_COLLIDE_MPR, fslot, 0) == 0;
+      if (b->D.nmprpair > 0 || b->F.p[MYO_F_GEOM_TYPE_OVR]) r &= tile(MYO_K_COLLIDE_MPR, fslot, 0) == 0;
       r &= tile(MYO_K_COLLIDE_COMPACT, fslot, 0) == 0;
     }
     return r;

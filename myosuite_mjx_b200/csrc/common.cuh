@@ -272,6 +272,32 @@ __device__ __noinline__ void comPos(int slot, SP sm, Tm t) {
   TSYNC();
 }
 
+// ------------------------------------------------------------------------------------------ per-world model overrides
+// geom_pos of geom g relative to its FRAME (the moving body its weld group hangs on): the compiled table, or -- when the
+// caller bound MYO_F_GEOM_POS_OVR and this world's entry is not NaN -- the world's own body-local position carried through
+// the body's constant offset to its frame (reference: reorient_sar_v0.py:241-245 rewrites geom_pos per episode).
+__device__ __forceinline__ f3 geomLocalPos(const DevModel& D, const void* posovr, World W, int g) {
+  if (posovr) {
+    const float x = OUTF(posovr, 3 * g);
+    if (x == x) {
+      const int b = D.geom_body[g];
+      return ld3(D.body_off_pos + 3 * b) + mulM(D.body_off_mat + 9 * b, mk3(x, OUTF(posovr, 3 * g + 1), OUTF(posovr, 3 * g + 2)));
+    }
+  }
+  return ld3(D.geom_lpos + 3 * g);
+}
+// bounding-sphere radius of a primitive (mj_setConst rule for geom_rbound)
+__device__ __forceinline__ float geomRbound(int type, f3 s) {
+  switch (type) {
+    case G_SPHERE: return s.x;
+    case G_CAPSULE: return s.x + s.y;
+    case G_ELLIPSOID: return fmaxf(s.x, fmaxf(s.y, s.z));
+    case G_CYLINDER: return sqrtf(s.x * s.x + s.y * s.y);
+    case G_BOX: return norm3(s);
+    default: return 0.f;
+  }
+}
+
 // ------------------------------------------------------------------------------------------ mjData position outputs
 // Written straight to global memory (struct-of-arrays, coalesced across the warp's worlds); nothing here feeds the dynamics.
 __device__ __noinline__ void writePositionOutputs(int slot, int fslot, SP sm, Tm t, World W) {
@@ -367,7 +393,7 @@ __device__ __noinline__ void writePositionOutputs(int slot, int fslot, SP sm, Tm
       const int f = D.geom_frame[g];
       auto R = FR_MAT(sm, L, f);
       if (gp) {
-        const f3 p = ld3(FR_POS(sm, L, f)) + mulM(R, ld3(D.geom_lpos + 3 * g));
+        const f3 p = ld3(FR_POS(sm, L, f)) + mulM(R, geomLocalPos(D, tP[slot].F.p[MYO_F_GEOM_POS_OVR], W, g));
         OUTF(gp, 3 * g) = p.x; OUTF(gp, 3 * g + 1) = p.y; OUTF(gp, 3 * g + 2) = p.z;
       }
       if (gm) {
@@ -868,6 +894,7 @@ __device__ __noinline__ void actuation(int slot, int fslot, SP sm, Tm t, World W
   const bool on = !(D.disableflags & DSBL_ACTUATION);
   void* olen = F.p[MYO_F_ACTUATOR_LENGTH]; void* ovel = F.p[MYO_F_ACTUATOR_VELOCITY]; void* ofrc = F.p[MYO_F_ACTUATOR_FORCE];
   void* odot = F.p[MYO_F_ACT_DOT];
+  const void* gsc = tP[slot].F.p[MYO_F_ACT_GAINSCALE];   // input: always the batch's own slot
   TFOR(i, nu) {
     const int id = D.act_trnid[i];
     const float gear = D.act_gear[i];
@@ -907,6 +934,7 @@ __device__ __noinline__ void actuation(int slot, int fslot, SP sm, Tm t, World W
         if (bt == BIAS_AFFINE) bias = bp[0] + bp[1] * len + bp[2] * vel;
         else if (bt == BIAS_MUSCLE) muscleGainBias(len, vel, D.act_lengthrange + 2 * i, D.act_acc0[i], bp, &tmp, &bias);
       }
+      if (gsc) gain *= OUTF(gsc, i);   // per-world muscle weakness (reference: base_v0.py:64-68 scales gainprm[:, 2])
       force = gain * a + bias;
       if (fl & ACT_FORCELIMITED) force = clipf(force, D.act_forcerange[2 * i], D.act_forcerange[2 * i + 1]);
     }
@@ -1056,20 +1084,31 @@ __device__ __forceinline__ Hit sphereSphere(f3 c1, float r1, f3 c2, float r2) {
   h.dist = n - r1 - r2; h.pos = c1 + h.nrm * (r1 + 0.5f * h.dist);
   return h;
 }
-// narrow phase for one candidate pair; returns the number of contacts (0..2) with dist < margin
+// effective shape of a collision geom: the compiled tables, or this world's cgshape record when shape overrides are bound
+struct CgShape { int type; f3 size; float rbound; };
+__device__ __forceinline__ CgShape cgShape(const DevModel& D, const SmemLayout& L, SP sm, bool ovr, int c) {
+  CgShape r;
+  if (ovr) { auto o = sm + L.cgshape + 5 * c; r.type = __float_as_int(o[0]); r.size = ld3(o + 1); r.rbound = o[4]; }
+  else { r.type = D.cg_type[c]; r.size = ld3(D.cg_size + 3 * c); r.rbound = D.cg_rbound[c]; }
+  return r;
+}
+#define MAXHIT 4   // contacts of one candidate pair: plane - box gives up to four, plane - capsule two, everything else one
+// narrow phase for one candidate pair; returns the number of contacts (0..MAXHIT) with dist < margin
 __device__ __noinline__ int collidePair(int slot, SP sm, int pr, Hit* h) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
   const int c1 = D.pair_cg1[pr], c2 = D.pair_cg2[pr];
-  const int t1 = D.cg_type[c1], t2 = D.cg_type[c2];
+  const bool ovr = tP[slot].F.p[MYO_F_GEOM_TYPE_OVR] != nullptr;
+  const CgShape S1 = cgShape(D, L, sm, ovr, c1), S2 = cgShape(D, L, sm, ovr, c2);
+  const int t1 = S1.type, t2 = S2.type;
   const float margin = D.pair_prm[16 * pr];
   auto P1 = sm + L.cgpose + 12 * c1; auto P2 = sm + L.cgpose + 12 * c2;
   const f3 p1 = ld3(P1), p2 = ld3(P2);
   const SP R1 = P1 + 3, R2 = P2 + 3;
-  const f3 sz1 = ld3(D.cg_size + 3 * c1), sz2 = ld3(D.cg_size + 3 * c2);
+  const f3 sz1 = S1.size, sz2 = S2.size;
   const f3 ax1 = mk3(R1[2], R1[5], R1[8]), ax2 = mk3(R2[2], R2[5], R2[8]);
   int n = 0;
   if (t1 == G_PLANE) {
-    if (dot(p2 - p1, ax1) > D.cg_rbound[c2] + margin) return 0;
+    if (dot(p2 - p1, ax1) > S2.rbound + margin) return 0;
     if (t2 == G_SPHERE || t2 == G_CAPSULE) {
       const int cnt = t2 == G_SPHERE ? 1 : 2;
       // #pragma unroll 1
@@ -1077,6 +1116,17 @@ __device__ __noinline__ int collidePair(int slot, SP sm, int pr, Hit* h) {
         const f3 c = t2 == G_SPHERE ? p2 : (k == 0 ? p2 + ax2 * sz2.y : p2 - ax2 * sz2.y);
         const float dist = dot(c - p1, ax1) - sz2.x;
         if (dist < margin) { h[n].dist = dist; h[n].pos = c - ax1 * (sz2.x + 0.5f * dist); h[n].nrm = ax1; n++; }
+      }
+    } else if (t2 == G_BOX) {
+      // mjc_PlaneBox: the corners below the box centre that are within the margin, in corner order, at most four
+      const float dist = dot(p2 - p1, ax1);
+      for (int i = 0; i < 8 && n < MAXHIT; i++) {
+        const f3 v = mk3((i & 1) ? sz2.x : -sz2.x, (i & 2) ? sz2.y : -sz2.y, (i & 4) ? sz2.z : -sz2.z);
+        const f3 corner = mulM(R2, v);
+        const float ld = dot(ax1, corner);
+        if (dist + ld > margin || ld > 0.f) continue;
+        const float cd = dist + ld;
+        h[n].dist = cd; h[n].pos = p2 + corner - ax1 * (0.5f * cd); h[n].nrm = ax1; n++;
       }
     } else {
       Shape s; s.type = t2; s.pos = mkd(p2.x, p2.y, p2.z); s.mat = R2; s.size = mkd(sz2.x, sz2.y, sz2.z); s.margin = 0.0;
@@ -1087,7 +1137,7 @@ __device__ __noinline__ int collidePair(int slot, SP sm, int pr, Hit* h) {
     }
     return n;
   }
-  if (norm3(p2 - p1) > D.cg_rbound[c1] + D.cg_rbound[c2] + margin) return 0;
+  if (norm3(p2 - p1) > S1.rbound + S2.rbound + margin) return 0;
   if (t1 == G_SPHERE && t2 == G_SPHERE) h[0] = sphereSphere(p1, sz1.x, p2, sz2.x);
   else if (t1 == G_SPHERE && t2 == G_CAPSULE) h[0] = sphereSphere(p1, sz1.x, p2 + ax2 * clipf(dot(p1 - p2, ax2), -sz2.y, sz2.y), sz2.x);
   else if (t1 == G_CAPSULE && t2 == G_CAPSULE) {

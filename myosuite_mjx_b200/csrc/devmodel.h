@@ -62,7 +62,7 @@ struct DevModel {
   // ---- bodies / geoms / sites (offsets relative to their frame)
   const int *body_frame, *body_root, *body_subend, *body_parent;
   const float *body_off_pos, *body_off_quat, *body_ipos, *body_iquat, *body_mass, *body_inertia, *body_subtreemass;
-  const int *geom_frame, *site_frame;
+  const int *geom_frame, *site_frame, *geom_body;
   const float *geom_lpos, *geom_lquat, *site_lpos, *site_lquat;
   const float *body_off_mat, *body_imat, *geom_lmat, *site_lmat;   // 3x3 row-major rotations of the offsets above
   // ---- tendons
@@ -122,7 +122,7 @@ struct SmemLayout {
   // overlay region A (tendon stage)
   int slots, ulen, uwrap, uwpt, gpre, upts, tmpbody;
   // overlay region B (collision / constraint / solver stage)
-  int cgpose, con, conJ, conU, conW, efc, H, Hsave, nvec, limrow, basev, cand, ctmp;
+  int cgpose, cgshape, con, conJ, conU, conW, efc, H, Hsave, nvec, limrow, basev, cand, ctmp;
   int nv;        // copy of DevModel.nv (the launch sizes the shared-memory Hessian tiles from it)
   int hshared;   // set by the kernel variant at upload: Newton Hessian tiles live in shared memory
   int wantw;     // set at upload: a path-point field is bound, the tendon stage keeps tangent points and wrap counts

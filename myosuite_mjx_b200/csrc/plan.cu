@@ -298,6 +298,7 @@ void myo_build_plan(const myo_model_desc& m, int nconmax_req, int njmax_req, Dev
       int b = m.site_bodyid[s]; sf[s] = body_frame[b];
       pushp(sp, add(off_pos[b], rot(off_quat[b], ldp(&m.site_pos[3 * s])))); pushq(sq, qnorm(qmul(off_quat[b], ldq(&m.site_quat[4 * s]))));
     }
+    { std::vector<int> gb(m.geom_bodyid, m.geom_bodyid + m.ngeom); D.geom_body = upload(gb, owned); }
     D.geom_frame = upload(gf, owned); D.site_frame = upload(sf, owned); D.geom_lpos = upload(gp, owned); D.geom_lquat = upload(gq, owned);
     D.site_lpos = upload(sp, owned); D.site_lquat = upload(sq, owned);
   }
@@ -659,14 +660,15 @@ void myo_make_layout(DevModel& D, int nconmax_req, int njmax_req, SmemLayout& L)
   endA = std::max(endA, o);
   o = endA;   // no overlay: the tendon, inertia and collision phases of a step run concurrently on separate streams (api.cu)
   // region B: collision, constraints, solver
-  L.cgpose = take(12 * D.ncg); L.con = take(12 * D.nconmax); L.conJ = take(nb * D.nconmax * nv); L.efc = take(10 * D.njmax);
+  L.cgpose = take(12 * D.ncg); L.cgshape = take(5 * D.ncg);   // cgshape: effective type, size[3], rbound (per-world overrides)
+  L.con = take(12 * D.nconmax); L.conJ = take(nb * D.nconmax * nv); L.efc = take(10 * D.njmax);
   // H: lower triangle + the factor's diagonal (tile.cu newtonKernel when its block does not fit shared memory)
   L.H = take(nv * nv + nv);
   L.Hsave = take(nv * (nv + 1) / 2);   // the unfactored Hessian, updated by the later Newton passes of a tile
   L.nvec = take(6 * nv);
   L.limrow = take(2 * (D.nlimj + D.nlimt));
   L.basev = take(2 * nb * D.nconmax);
-  L.cand = take(D.npair); L.ctmp = take(16 * D.npair);   // survivor list and per-survivor narrow-phase records
+  L.cand = take(D.npair); L.ctmp = take(32 * D.npair);   // survivor list and per-survivor narrow-phase records
   L.conU = take(nb * D.nconmax * nv);   // W Jb of the Newton Hessian (tile.cu hessianTile)
   L.conW = take(8 * D.nconmax);         // per-contact weights of the active pyramid rows in base-row space
   int endB = o;

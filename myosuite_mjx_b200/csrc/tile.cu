@@ -160,25 +160,27 @@ __global__ void __launch_bounds__(32 * MAXW, MINB_VELACT) velactKernel(int slot,
 // survivors starting at its lane's exclusive prefix.  The convex narrow phase (MPR, float64, long) is listed per lane
 // first and run afterwards, so the lanes of a warp that have an MPR pair run it at the same time.
 
-__device__ __forceinline__ bool broadPass(const DevModel& D, const SmemLayout& L, SP sm, int pr) {
+__device__ __forceinline__ bool broadPass(const DevModel& D, const SmemLayout& L, SP sm, bool ovr, int pr) {
   const int c1 = D.pair_cg1[pr], c2 = D.pair_cg2[pr];
   auto P1 = sm + L.cgpose + 12 * c1; auto P2 = sm + L.cgpose + 12 * c2;
   const f3 d = ld3(P2) - ld3(P1);
   const float margin = D.pair_prm[16 * pr];
-  if (D.cg_type[c1] == G_PLANE) return !(d.x * P1[5] + d.y * P1[8] + d.z * P1[11] > D.cg_rbound[c2] + margin);
-  const float r = D.cg_rbound[c1] + D.cg_rbound[c2] + margin;
+  const float r1 = ovr ? sm[L.cgshape + 5 * c1 + 4] : D.cg_rbound[c1], r2 = ovr ? sm[L.cgshape + 5 * c2 + 4] : D.cg_rbound[c2];
+  if (D.cg_type[c1] == G_PLANE) return !(d.x * P1[5] + d.y * P1[8] + d.z * P1[11] > r2 + margin);   // (a plane stays a plane)
+  const float r = r1 + r2 + margin;
   return !(dot(d, d) > r * r);
 }
 
-__device__ __forceinline__ bool isMprPair(const DevModel& D, int pr) {
-  const int t1 = D.cg_type[D.pair_cg1[pr]], t2 = D.cg_type[D.pair_cg2[pr]];
+__device__ __forceinline__ bool isMprPair(const DevModel& D, const SmemLayout& L, SP sm, bool ovr, int pr) {
+  const int c1 = D.pair_cg1[pr], c2 = D.pair_cg2[pr];
+  const int t1 = ovr ? __float_as_int(sm[L.cgshape + 5 * c1]) : D.cg_type[c1], t2 = ovr ? __float_as_int(sm[L.cgshape + 5 * c2]) : D.cg_type[c2];
   return t1 != G_PLANE && !((t1 == G_SPHERE || t1 == G_CAPSULE) && (t2 == G_SPHERE || t2 == G_CAPSULE) && !(t1 == G_CAPSULE && t2 == G_SPHERE));
 }
 // collide A: geom poses, broad phase (ordered survivor list per lane), closed-form narrow phase.  Survivors that need the
 // convex narrow phase (MPR: float64, long, data-dependent) are appended to a batch-wide work list instead: a tile has a
 // handful of them per world at different survivor positions, so inside the tile they would run at a few active lanes
 // while the other warps wait; collideMprKernel runs them one pair per LANE.  Per-survivor result record in L.ctmp:
-// 16 floats = hit count, up to two hits (dist, pos, normal).
+// 32 floats = hit count, up to MAXHIT hits (dist, pos, normal).
 __global__ void __launch_bounds__(32 * MAXW, MINB_COLLIDE) collideKernel(int slot, int nworld, const int* __restrict__ mask, float* __restrict__ scratch) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L; const TileAux& X = tP[slot].X;
   Ctx c = tileCtx(slot, nworld, mask, scratch);
@@ -190,10 +192,23 @@ __global__ void __launch_bounds__(32 * MAXW, MINB_COLLIDE) collideKernel(int slo
     if (t.tl == 0) { sm[L.counts] = __int_as_float(0); sm[L.counts + 3] = __int_as_float(0); }
     return;
   }
+  const FieldPtrs& Fin = tP[slot].F;
+  const void* tovr = Fin.p[MYO_F_GEOM_TYPE_OVR]; const void* sovr = Fin.p[MYO_F_GEOM_SIZE_OVR]; const void* povr = Fin.p[MYO_F_GEOM_POS_OVR];
+  const bool ovr = tovr != nullptr;   // shapes are per world: the narrow phase reads this world's cgshape records
+  const World W = c.W;
   TFOR(g, D.ncg) {
-    const int f = D.cg_frame[g];
+    const int f = D.cg_frame[g], gid = D.cg_geom[g];
     auto o = sm + L.cgpose + 12 * g;
-    st3(o, ld3(FR_POS(sm, L, f)) + mulM(FR_MAT(sm, L, f), ld3(D.cg_lpos + 3 * g)));
+    st3(o, ld3(FR_POS(sm, L, f)) + mulM(FR_MAT(sm, L, f), povr ? geomLocalPos(D, povr, c.W, gid) : ld3(D.cg_lpos + 3 * g)));
+    if (ovr) {
+      int type = D.cg_type[g]; f3 size = ld3(D.cg_size + 3 * g); float rb = D.cg_rbound[g];
+      const int to = OUTI(tovr, gid);
+      if (to >= 0 && type != G_PLANE) type = to;
+      if (sovr && OUTF(sovr, 3 * gid) > 0.f) size = mk3(OUTF(sovr, 3 * gid), OUTF(sovr, 3 * gid + 1), OUTF(sovr, 3 * gid + 2));
+      if (to >= 0 || (sovr && OUTF(sovr, 3 * gid) > 0.f)) rb = geomRbound(type, size);
+      auto sh = sm + L.cgshape + 5 * g;
+      sh[0] = __int_as_float(type); st3(sh + 1, size); sh[4] = rb;
+    }
     float M[9]; mulMM(M, FR_MAT(sm, L, f), D.cg_lmat + 9 * g);
 #pragma unroll
     for (int k = 0; k < 9; k++) o[3 + k] = M[k];
@@ -205,12 +220,12 @@ __global__ void __launch_bounds__(32 * MAXW, MINB_COLLIDE) collideKernel(int slo
   {
     const int chunk = (D.npair + nw - 1) / nw, p0 = t.tl * chunk, p1 = min(D.npair, p0 + chunk);
     int cnt = 0;
-    for (int pr = p0; pr < p1; pr++) cnt += broadPass(D, L, sm, pr) ? 1 : 0;
+    for (int pr = p0; pr < p1; pr++) cnt += broadPass(D, L, sm, ovr, pr) ? 1 : 0;
     sCnt[t.tl][lane] = cnt;
     TSYNC();
     int off = 0; ncand = 0;
     for (int j = 0; j < nw; j++) { const int v = sCnt[j][lane]; if (j < t.tl) off += v; ncand += v; }
-    for (int pr = p0; pr < p1; pr++) if (broadPass(D, L, sm, pr)) cand[off++] = pr;
+    for (int pr = p0; pr < p1; pr++) if (broadPass(D, L, sm, ovr, pr)) cand[off++] = pr;
     TSYNC();
   }
   if (t.tl == 0) sm[L.counts + 3] = __int_as_float(ncand);
@@ -219,11 +234,11 @@ __global__ void __launch_bounds__(32 * MAXW, MINB_COLLIDE) collideKernel(int slo
   const int w = (int)c.W.w;
   for (int k = t.tl; k < ncand; k += nw) {
     const int pr = cand[k];
-    const bool mp = isMprPair(D, pr);
+    const bool mp = isMprPair(D, L, sm, ovr, pr);
     if (!mp) {
-      Hit h[2];
+      Hit h[MAXHIT];
       const int n = collidePair(slot, sm, pr, h);
-      auto o = tmp + 16 * k;
+      auto o = tmp + 32 * k;
       o[0] = __int_as_float(n);
       for (int q = 0; q < n; q++) { o[1 + 7 * q] = h[q].dist; st3(o + 2 + 7 * q, h[q].pos); st3(o + 5 + 7 * q, h[q].nrm); }
     }
@@ -250,9 +265,9 @@ __global__ void __launch_bounds__(128) collideMprKernel(int slot, float* __restr
     const int2 e = X.mpr_list[i];
     SP sm; sm.p = scratch + (size_t)(e.x >> 5) * L.total * SCR + (e.x & 31);
     const int pr = __float_as_int(sm[L.cand + e.y]);
-    Hit h[2];
+    Hit h[MAXHIT];
     const int nh = collidePair(slot, sm, pr, h);
-    auto o = sm + L.ctmp + 16 * e.y;
+    auto o = sm + L.ctmp + 32 * e.y;
     o[0] = __int_as_float(nh);
     if (nh) { o[1] = h[0].dist; st3(o + 2, h[0].pos); st3(o + 5, h[0].nrm); }
   }
@@ -273,17 +288,17 @@ __global__ void __launch_bounds__(32 * MAXW, 2) collideCompactKernel(int slot, i
   const int ncand = __float_as_int(sm[L.counts + 3]);
   const int kc = (__reduce_max_sync(lmask, ncand) + nw - 1) / nw, k0 = min(ncand, t.tl * kc), k1 = min(ncand, k0 + kc);
   int cnt = 0;
-  for (int k = k0; k < k1; k++) cnt += __float_as_int(tmp[16 * k]);
+  for (int k = k0; k < k1; k++) cnt += __float_as_int(tmp[32 * k]);
   sCnt[t.tl][lane] = cnt;
   TSYNC();
   int at = 0, ncon = 0;
   for (int j = 0; j < nw; j++) { const int v = sCnt[j][lane]; if (j < t.tl) at += v; ncon += v; }
   for (int k = k0; k < k1; k++) {
-    const int n = __float_as_int(tmp[16 * k]);
+    const int n = __float_as_int(tmp[32 * k]);
     for (int q = 0; q < n; q++, at++) {
       if (at >= D.nconmax) continue;
       const int pr = cand[k];
-      auto cr = sm + L.con + 12 * at; auto o = tmp + 16 * k + 1 + 7 * q;
+      auto cr = sm + L.con + 12 * at; auto o = tmp + 32 * k + 1 + 7 * q;
       for (int e = 0; e < 7; e++) cr[e] = o[e];
       cr[7] = __int_as_float(pr); cr[8] = __int_as_float(-1); cr[9] = __int_as_float(D.pair_dim[pr]);
       // dofs that move exactly one of the two bodies (static per pair): the only non-zero columns of the contact's rows

@@ -30,7 +30,11 @@ from . import mjcf as _mjcf
 STATE_FIELDS = ("qpos", "qvel", "act", "ctrl", "time", "qacc_warmstart", "status")
 # the subset a policy loop needs ("mode B" in DESIGN.md)
 CORE_FIELDS = STATE_FIELDS + ("qacc", "actuator_force", "actuator_length", "actuator_velocity")
-INPUT_FIELDS = ("qfrc_applied",)   # optional inputs: bound only on request (an unbound input reads as zero)
+# optional inputs: bound only on request.  qfrc_applied reads as zero when unbound; the per-world MODEL overrides
+# (include/myostep.h: the reference's envs rewrite mjModel per episode, reorient_sar_v0.py:207-245, base_v0.py:64-68) read as
+# "the compiled model's value" when unbound and start at their keep values when bound
+INPUT_FIELDS = ("qfrc_applied", "geom_type_ovr", "geom_size_ovr", "geom_pos_ovr", "act_gainscale")
+_OVR_FILL = {"geom_type_ovr": -1, "geom_size_ovr": -1.0, "geom_pos_ovr": float("nan"), "act_gainscale": 1.0}
 
 _SHAPES = {
     "xpos": ("nbody", 3), "xquat": ("nbody", 4), "xmat": ("nbody", 9), "xipos": ("nbody", 3), "ximat": ("nbody", 9),
@@ -39,7 +43,7 @@ _SHAPES = {
     "crb": ("nbody", 10), "cdof": ("nv", 6), "cdof_dot": ("nv", 6), "cvel": ("nbody", 6), "ten_j": ("ntendon", "nv"),
     "actuator_moment": ("nu", "nv"), "qm": ("nv", "nv"), "qld": ("nv", "nv"), "contact_geom": (-1, 2), "contact_pos": (-1, 3),
     "contact_frame": (-1, 9), "contact_friction": (-1, 5), "contact_solref": (-1, 2), "contact_solimp": (-1, 5),
-    "efc_j": (-1, "nv"), "wrap_obj": (-1, 2), "wrap_xpos": (-1, 6),
+    "efc_j": (-1, "nv"), "wrap_obj": (-1, 2), "wrap_xpos": (-1, 6), "geom_size_ovr": ("ngeom", 3), "geom_pos_ovr": ("ngeom", 3),
 }
 
 
@@ -99,7 +103,7 @@ class Data:
             if cnt == 0:
                 continue
             dt = torch.int32 if L.myo_field_is_int(fid) else torch.float32
-            self.bind(name, torch.zeros((cnt, self.nworld), dtype=dt, device=dev))
+            self.bind(name, torch.full((cnt, self.nworld), _OVR_FILL.get(name, 0), dtype=dt, device=dev))
 
     # -- zero-copy binding of caller-owned device memory (torch tensor or anything exporting __dlpack__)
     def bind(self, name, tensor):

@@ -818,7 +818,22 @@ template <typename T> struct Oracle {
       };
       if (t2 == G_SPHERE) planeSphere(p2, sz2.x);
       else if (t2 == G_CAPSULE) { planeSphere(p2 + ax2 * sz2.y, sz2.x); planeSphere(p2 - ax2 * sz2.y, sz2.x); }
-      else {  // ellipsoid, cylinder, box: deepest support point along -normal (single contact)
+      else if (t2 == G_BOX) {
+        // mjc_PlaneBox (MuJoCo engine_collision_primitive.c, restated): the corners below the box centre that lie within the
+        // margin become contacts, in corner order (bit 0 of the index = x), at most four
+        T dist = dot(p2 - p1, ax1);
+        int cnt = 0;
+        for (int i = 0; i < 8 && cnt < 4; i++) {
+          V3<T> v{(i & 1) ? sz2.x : -sz2.x, (i & 2) ? sz2.y : -sz2.y, (i & 4) ? sz2.z : -sz2.z};
+          V3<T> corner = mulM(R2, v);
+          T ld = dot(ax1, corner);
+          if (dist + ld > pp.margin || ld > 0) continue;
+          T cd = dist + ld;
+          addContact(g1, g2, pp, cd, p2 + corner - ax1 * (cd / 2), ax1);
+          cnt++;
+        }
+      }
+      else {  // ellipsoid, cylinder: deepest support point along -normal (single contact)
         Shape<T> s{t2, p2, R2, sz2, 0};
         V3<T> sp = support(s, ax1 * T(-1));
         T dist = dot(sp - p1, ax1);
