@@ -1092,13 +1092,19 @@ __device__ __forceinline__ CgShape cgShape(const DevModel& D, const SmemLayout& 
   else { r.type = D.cg_type[c]; r.size = ld3(D.cg_size + 3 * c); r.rbound = D.cg_rbound[c]; }
   return r;
 }
+// contact record word 7: the candidate pair, with bit 30 set when this world's shape overrides put the pair's geoms in the
+// other order (MuJoCo calls the collision function with the lower geom type first: geom1 / geom2 and the normal follow)
+#define CON_PAIR(x) ((x) & 0x3fffffff)
+#define CON_SWAP(x) (((x) >> 30) & 1)
 #define MAXHIT 4   // contacts of one candidate pair: plane - box gives up to four, plane - capsule two, everything else one
 // narrow phase for one candidate pair; returns the number of contacts (0..MAXHIT) with dist < margin
-__device__ __noinline__ int collidePair(int slot, SP sm, int pr, Hit* h) {
+__device__ __noinline__ int collidePair(int slot, SP sm, int pr, Hit* h, int* swapped) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
-  const int c1 = D.pair_cg1[pr], c2 = D.pair_cg2[pr];
+  int c1 = D.pair_cg1[pr], c2 = D.pair_cg2[pr];
   const bool ovr = tP[slot].F.p[MYO_F_GEOM_TYPE_OVR] != nullptr;
-  const CgShape S1 = cgShape(D, L, sm, ovr, c1), S2 = cgShape(D, L, sm, ovr, c2);
+  CgShape S1 = cgShape(D, L, sm, ovr, c1), S2 = cgShape(D, L, sm, ovr, c2);
+  *swapped = 0;
+  if (S1.type > S2.type) { const int c = c1; c1 = c2; c2 = c; const CgShape S = S1; S1 = S2; S2 = S; *swapped = 1; }   // only through an override: the compiled list is ordered
   const int t1 = S1.type, t2 = S2.type;
   const float margin = D.pair_prm[16 * pr];
   auto P1 = sm + L.cgpose + 12 * c1; auto P2 = sm + L.cgpose + 12 * c2;
@@ -1203,9 +1209,12 @@ __device__ __noinline__ void writeConstraintOutputs(int slot, int fslot, SP sm, 
     TFOR(c, ncm) {
       const bool on = c < ncon;
       auto cr = sm + L.con + 12 * c;
-      const int pr = on ? __float_as_int(cr[7]) : 0;
+      const int prw = on ? __float_as_int(cr[7]) : 0, pr = CON_PAIR(prw), sw = CON_SWAP(prw);
       auto pp = D.pair_prm + 16 * pr;
-      if (cg) { OUTI(cg, 2 * c) = on ? D.cg_geom[D.pair_cg1[pr]] : -1; OUTI(cg, 2 * c + 1) = on ? D.cg_geom[D.pair_cg2[pr]] : -1; }
+      if (cg) {
+        const int ga = on ? D.cg_geom[D.pair_cg1[pr]] : -1, gb = on ? D.cg_geom[D.pair_cg2[pr]] : -1;
+        OUTI(cg, 2 * c) = sw ? gb : ga; OUTI(cg, 2 * c + 1) = sw ? ga : gb;
+      }
       if (cdim) OUTI(cdim, c) = on ? __float_as_int(cr[9]) : 0;
       if (cadr) OUTI(cadr, c) = on ? __float_as_int(cr[8]) : -1;
       if (cdist) OUTF(cdist, c) = on ? cr[0] : 0.f;
@@ -1451,9 +1460,9 @@ __device__ __noinline__ void touchSensors(int slot, int fslot, SP sm, Tm t, Worl
     float total = 0.f;
     for (int c = 0; c < ncon; c++) {
       auto cr = sm + L.con + 12 * c;
-      const int adr = __float_as_int(cr[8]), dim = __float_as_int(cr[9]), pr = __float_as_int(cr[7]);
+      const int adr = __float_as_int(cr[8]), dim = __float_as_int(cr[9]), prw = __float_as_int(cr[7]), pr = CON_PAIR(prw);
       if (adr < 0) continue;
-      const int b1 = D.cg_body[D.pair_cg1[pr]], b2 = D.cg_body[D.pair_cg2[pr]];
+      const int b1 = D.cg_body[CON_SWAP(prw) ? D.pair_cg2[pr] : D.pair_cg1[pr]], b2 = D.cg_body[CON_SWAP(prw) ? D.pair_cg1[pr] : D.pair_cg2[pr]];
       if (body != b1 && body != b2) continue;
       float fn = 0.f;
       const int rows = dim == 1 ? 1 : 2 * (dim - 1);

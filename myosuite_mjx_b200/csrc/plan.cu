@@ -627,7 +627,7 @@ void myo_build_plan(const myo_model_desc& m, int nconmax_req, int njmax_req, Dev
 // Per-batch capacities (nconmax, njmax) and the per-world shared-memory layout that follows from them.
 void myo_make_layout(DevModel& D, int nconmax_req, int njmax_req, SmemLayout& L) {
   const int nv = D.nv;
-  int maxcon = 2 * D.npair;  // 2 contacts per plane-capsule pair, 1 otherwise
+  int maxcon = 4 * D.npair;  // up to 4 contacts per plane-box pair, 2 per plane-capsule pair, 1 otherwise
   // defaults sized from the MyoHand random-ctrl rollout (fist clench): max 27 contacts / 123 rows over 8192 worlds x 1000 steps
   D.nconmax = nconmax_req > 0 ? nconmax_req : std::min(maxcon, 32);
   int maxrows = D.neq + 2 * D.nlimj + 2 * D.nlimt + D.nconmax * (D.maxbase == 1 ? 1 : 2 * (D.maxbase - 1));

@@ -237,9 +237,10 @@ __global__ void __launch_bounds__(32 * MAXW, MINB_COLLIDE) collideKernel(int slo
     const bool mp = isMprPair(D, L, sm, ovr, pr);
     if (!mp) {
       Hit h[MAXHIT];
-      const int n = collidePair(slot, sm, pr, h);
+      int sw;
+      const int n = collidePair(slot, sm, pr, h, &sw);
       auto o = tmp + 32 * k;
-      o[0] = __int_as_float(n);
+      o[0] = __int_as_float(n | (sw << 8));
       for (int q = 0; q < n; q++) { o[1 + 7 * q] = h[q].dist; st3(o + 2 + 7 * q, h[q].pos); st3(o + 5 + 7 * q, h[q].nrm); }
     }
     const unsigned act = __activemask();
@@ -266,9 +267,10 @@ __global__ void __launch_bounds__(128) collideMprKernel(int slot, float* __restr
     SP sm; sm.p = scratch + (size_t)(e.x >> 5) * L.total * SCR + (e.x & 31);
     const int pr = __float_as_int(sm[L.cand + e.y]);
     Hit h[MAXHIT];
-    const int nh = collidePair(slot, sm, pr, h);
+    int sw;
+    const int nh = collidePair(slot, sm, pr, h, &sw);
     auto o = sm + L.ctmp + 32 * e.y;
-    o[0] = __int_as_float(nh);
+    o[0] = __int_as_float(nh | (sw << 8));
     if (nh) { o[1] = h[0].dist; st3(o + 2, h[0].pos); st3(o + 5, h[0].nrm); }
   }
 }
@@ -288,19 +290,19 @@ __global__ void __launch_bounds__(32 * MAXW, 2) collideCompactKernel(int slot, i
   const int ncand = __float_as_int(sm[L.counts + 3]);
   const int kc = (__reduce_max_sync(lmask, ncand) + nw - 1) / nw, k0 = min(ncand, t.tl * kc), k1 = min(ncand, k0 + kc);
   int cnt = 0;
-  for (int k = k0; k < k1; k++) cnt += __float_as_int(tmp[32 * k]);
+  for (int k = k0; k < k1; k++) cnt += __float_as_int(tmp[32 * k]) & 0xff;
   sCnt[t.tl][lane] = cnt;
   TSYNC();
   int at = 0, ncon = 0;
   for (int j = 0; j < nw; j++) { const int v = sCnt[j][lane]; if (j < t.tl) at += v; ncon += v; }
   for (int k = k0; k < k1; k++) {
-    const int n = __float_as_int(tmp[32 * k]);
+    const int nsw = __float_as_int(tmp[32 * k]), n = nsw & 0xff, sw = nsw >> 8;
     for (int q = 0; q < n; q++, at++) {
       if (at >= D.nconmax) continue;
       const int pr = cand[k];
       auto cr = sm + L.con + 12 * at; auto o = tmp + 32 * k + 1 + 7 * q;
       for (int e = 0; e < 7; e++) cr[e] = o[e];
-      cr[7] = __int_as_float(pr); cr[8] = __int_as_float(-1); cr[9] = __int_as_float(D.pair_dim[pr]);
+      cr[7] = __int_as_float(pr | (sw << 30)); cr[8] = __int_as_float(-1); cr[9] = __int_as_float(D.pair_dim[pr]);
       // dofs that move exactly one of the two bodies (static per pair): the only non-zero columns of the contact's rows
       const int f1 = D.cg_frame[D.pair_cg1[pr]], f2 = D.cg_frame[D.pair_cg2[pr]];
       cr[10] = __int_as_float(D.fr_mask[2 * f1] ^ D.fr_mask[2 * f2]); cr[11] = __int_as_float(D.fr_mask[2 * f1 + 1] ^ D.fr_mask[2 * f2 + 1]);
@@ -366,7 +368,7 @@ __device__ __forceinline__ void limitState(const DevModel& D, const SmemLayout& 
 }
 __device__ __forceinline__ int contactRows(const DevModel& D, const SmemLayout& L, SP sm, int c) {
   auto cr = sm + L.con + 12 * c;
-  const int pr = __float_as_int(cr[7]), dim = __float_as_int(cr[9]);
+  const int pr = CON_PAIR(__float_as_int(cr[7])), dim = __float_as_int(cr[9]);
   const float inc = D.pair_prm[16 * pr] - D.pair_prm[16 * pr + 1];
   return cr[0] < inc ? (dim == 1 ? 1 : 2 * (dim - 1)) : 0;
 }
@@ -446,7 +448,8 @@ __device__ __noinline__ int makeConstraintTile(int slot, SP sm, Tm t, int ncon, 
         continue;
       }
       const unsigned mlo = (unsigned)__float_as_int(cr[10]), mhi = (unsigned)__float_as_int(cr[11]);
-      const int f1 = D.cg_frame[D.pair_cg1[__float_as_int(cr[7])]];
+      const int prw = __float_as_int(cr[7]);
+      const int f1 = D.cg_frame[CON_SWAP(prw) ? D.pair_cg2[CON_PAIR(prw)] : D.pair_cg1[CON_PAIR(prw)]];
       const unsigned f1lo = (unsigned)D.fr_mask[2 * f1], f1hi = (unsigned)D.fr_mask[2 * f1 + 1];
       const f3 pos = ld3(cr + 1), n = ld3(cr + 4);
       f3 y, z; makeFrame(n, &y, &z);
@@ -473,7 +476,7 @@ __device__ __noinline__ int makeConstraintTile(int slot, SP sm, Tm t, int ncon, 
       auto cr = sm + L.con + 12 * c;
       const int adr = __float_as_int(cr[8]);
       if (adr < 0) continue;
-      const int pr = __float_as_int(cr[7]), dim = __float_as_int(cr[9]);
+      const int pr = CON_PAIR(__float_as_int(cr[7])), dim = __float_as_int(cr[9]);
       auto pp = D.pair_prm + 16 * pr;
       const float margin = pp[0] - pp[1], dist = cr[0];
       const int g1 = D.pair_cg1[pr], g2 = D.pair_cg2[pr];

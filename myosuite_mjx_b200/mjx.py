@@ -70,6 +70,20 @@ class Model:
             pass
 
 
+class _Batch:
+    """Owns one library batch and its buffer sets (two when the functional step ping-pongs).  `Data` objects are light views
+    of one set; the batch does not reference them, so it is destroyed as soon as the last view goes."""
+
+    def __init__(self, h):
+        self.h, self.sets, self.bound = h, [{}, None], 0
+
+    def __del__(self):
+        try:
+            _lib.lib().myo_batch_destroy(self.h)
+        except Exception:
+            pass
+
+
 class Data:
     """A batch of `nworld` worlds (vmapped mjx.Data counterpart).  Attributes are torch tensors `[nworld, ...]`."""
 
@@ -79,17 +93,13 @@ class Data:
         self.nworld = int(nworld)
         h = ctypes.c_void_p()
         _lib.check(L.myo_batch_create(model._h, self.nworld, int(nconmax), int(njmax), ctypes.byref(h)))
-        self._h = h
+        self._core, self._idx = _Batch(h), 0
         self.nconmax = L.myo_batch_nconmax(h)
         self.njmax = L.myo_batch_njmax(h)
         self.smem_bytes = L.myo_batch_smem_bytes(h)
         self.team = L.myo_batch_team(h)
         self.ctas_per_sm = L.myo_batch_ctas_per_sm(h)
         self.engine = "phase" if L.myo_batch_engine(h) == 1 else "mono"
-        self._t = {}
-        # several Data objects can share one batch handle (the two buffer sets of the functional step): `bound` is the one
-        # whose buffers the library currently writes, `refs` counts the sharers
-        self._share = {"bound": self, "refs": 1}
         dev = torch.device("cuda", model.device)
         if fields == "all":
             names = [n.lower() for n in _desc.FIELD_NAMES if n.lower() not in INPUT_FIELDS]
@@ -105,6 +115,14 @@ class Data:
             dt = torch.int32 if L.myo_field_is_int(fid) else torch.float32
             self.bind(name, torch.full((cnt, self.nworld), _OVR_FILL.get(name, 0), dtype=dt, device=dev))
 
+    @property
+    def _h(self):
+        return self._core.h
+
+    @property
+    def _t(self):
+        return self._core.sets[self._idx]
+
     # -- zero-copy binding of caller-owned device memory (torch tensor or anything exporting __dlpack__)
     def bind(self, name, tensor):
         """`tensor`: contiguous CUDA storage `[k, nworld]` (world fastest), or its `[nworld, k]` transposed view."""
@@ -116,28 +134,25 @@ class Data:
             raise ValueError("bound buffers must be contiguous [k, nworld] CUDA tensors")
         fid = _desc.FIELD_ID[name.lower()]
         self._t[name.lower()] = tensor
-        if self._share["bound"] is self:
+        if self._core.bound == self._idx:
             _lib.check(_lib.lib().myo_batch_bind(self._h, fid, ctypes.c_void_p(tensor.data_ptr()), tensor.numel() * tensor.element_size()))
 
     def _ensure_bound(self):
-        """make this object's buffers the ones the library reads and writes (no-op unless a partner set is bound)"""
-        if self._share["bound"] is not self:
+        """make this view's buffers the ones the library reads and writes (no-op unless the other set is bound)"""
+        if self._core.bound != self._idx:
             L = _lib.lib()
             for k, t in self._t.items():
                 _lib.check(L.myo_batch_bind(self._h, _desc.FIELD_ID[k], ctypes.c_void_p(t.data_ptr()), t.numel() * t.element_size()))
-            self._share["bound"] = self
+            self._core.bound = self._idx
 
     def _partner(self):
-        """the other buffer set of the ping-pong (allocated on first use): same batch, same fields, its own tensors"""
-        p = self.__dict__.get("_pong")
-        if p is None:
-            p = Data.__new__(Data)
-            for k in ("model", "nworld", "_h", "nconmax", "njmax", "smem_bytes", "team", "ctas_per_sm", "engine", "_share"):
-                p.__dict__[k] = self.__dict__[k]
-            p.__dict__["_t"] = {k: torch.zeros_like(v) for k, v in self._t.items()}
-            p.__dict__["_pong"] = self
-            self.__dict__["_pong"] = p
-            self._share["refs"] += 1
+        """a view of the other buffer set of the ping-pong (allocated on first use): same batch, same fields, its own tensors"""
+        other = self._idx ^ 1
+        if self._core.sets[other] is None:
+            self._core.sets[other] = {k: torch.zeros_like(v) for k, v in self._t.items()}
+        p = Data.__new__(Data)
+        p.__dict__.update({k: v for k, v in self.__dict__.items() if k != "_idx"})
+        p.__dict__["_idx"] = other
         return p
 
     def set_pipelined(self, on=True):
@@ -155,7 +170,8 @@ class Data:
             _lib.check(_lib.lib().myo_outputs_join(self._h, _stream()))
 
     def __getattr__(self, name):
-        t = self.__dict__.get("_t", {})
+        core = self.__dict__.get("_core")
+        t = core.sets[self.__dict__.get("_idx", 0)] if core is not None else {}
         key = {"q": "qpos", "qd": "qvel"}.get(name, name.lower())   # brax State aliases (myodm_v0.py:201-202)
         if key in t:
             self.join()
@@ -182,28 +198,16 @@ class Data:
         return list(self._t)
 
     def clone(self):
+        """an independent batch with copies of every bound buffer"""
         d = Data.__new__(Data)
         L = _lib.lib()
-        d.model, d.nworld = self.model, self.nworld
         h = ctypes.c_void_p()
         _lib.check(L.myo_batch_create(self.model._h, self.nworld, self.nconmax, self.njmax, ctypes.byref(h)))
-        d._h, d.nconmax, d.njmax, d._t = h, self.nconmax, self.njmax, {}
-        d.__dict__["_share"] = {"bound": d, "refs": 1}
-        d.smem_bytes, d.team, d.ctas_per_sm = self.smem_bytes, L.myo_batch_team(h), 1
-        d.engine = "phase" if L.myo_batch_engine(h) == 1 else "mono"
-        if self.__dict__.get("_pipelined"):
-            d.set_pipelined(True)
+        d.__dict__.update({k: v for k, v in self.__dict__.items() if k not in ("_core", "_idx")})
+        d.__dict__["_core"], d.__dict__["_idx"] = _Batch(h), 0
         for k, v in self._t.items():
             d.bind(k, v.clone())
         return d
-
-    def __del__(self):
-        try:
-            self._share["refs"] -= 1
-            if self._share["refs"] <= 0:
-                _lib.lib().myo_batch_destroy(self._h)
-        except Exception:
-            pass
 
 
 def _stream():

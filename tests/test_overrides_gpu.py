@@ -34,6 +34,7 @@ def test_object_shape_per_world_matches_edited_models(models):
     obj, top, bot = gnames.index("obj"), gnames.index("top"), gnames.index("bot")
     nw = 48
     qpos, qvel, act, ctrl = parity.random_state(m, nw, 11, qpos_spread=0.9)
+    qpos[:, 23:] = 0.0                               # the object where the XML puts it, the fingers around (and partly inside) it
     model = mjx.put_model(m)
     d = mjx.put_data(model, dict(qpos=qpos, qvel=0 * qvel, act=act, ctrl=ctrl), nworld=nw,
                      fields=list(mjx.CORE_FIELDS) + ["ncon", "nefc", "contact_geom", "contact_dist", "contact_pos", "geom_xpos", "qacc", "efc_force",
@@ -47,12 +48,10 @@ def test_object_shape_per_world_matches_edited_models(models):
         tp, bp = _top_bot(t, s)
         d.geom_pos_ovr[w, top] = torch.tensor(tp, dtype=torch.float32, device="cuda")
         d.geom_pos_ovr[w, bot] = torch.tensor(bp, dtype=torch.float32, device="cuda")
-    # let the object settle into the hand / onto the table for a while, then compare a forward pass from the GPU's own state
-    mjx.step(model, d, 150)
     mjx.forward(model, d)
     torch.cuda.synchronize()
-    assert int((d.status & ~1).abs().max()) == 0
-    q, v, a, ws = (getattr(d, f).double().cpu().numpy() for f in ("qpos", "qvel", "act", "qacc_warmstart"))
+    assert int(d.status.abs().max()) == 0
+    q, v, a = qpos, 0 * qvel, act
     with_obj, boxes = 0, 0
     for w in range(nw):
         mm = m
@@ -62,7 +61,7 @@ def test_object_shape_per_world_matches_edited_models(models):
             mm.geom_type[obj] = t; mm.geom_size[obj] = s; mm.geom_rbound[obj] = _rbound(t, s)
             mm.geom_pos[top], mm.geom_pos[bot] = _top_bot(t, s)
         o = oracle.Oracle(mm)
-        o.set_state(q[w], v[w], a[w], ctrl[w], np.zeros(m.nv)); o.forward()
+        o.reset(); o.set_state(q[w], v[w], a[w], ctrl[w], np.zeros(m.nv)); o.forward()
         n = o.ncon
         assert int(d.ncon[w, 0]) == n, f"world {w} ({shape[w]}): ncon {int(d.ncon[w, 0])} vs {n}"
         cg = np.asarray(o.contact_geom).reshape(-1, 2)
@@ -71,7 +70,7 @@ def test_object_shape_per_world_matches_edited_models(models):
         np.testing.assert_allclose(d.geom_xpos[w, [top, bot]].cpu().numpy(), np.asarray(o.geom_xpos).reshape(-1, 3)[[top, bot]], atol=2e-5)
         hit = (cg == obj).any()
         with_obj += int(hit); boxes += int(hit and w < 40 and shape[w][0] == 6)
-    assert with_obj >= nw // 3 and boxes >= 2, f"too few worlds touch the object ({with_obj}, boxes {boxes}): the test poses need attention"
+    assert with_obj >= nw // 3 and boxes >= 4, f"too few worlds touch the object ({with_obj}, boxes {boxes}): the test poses need attention"
 
 
 def test_box_rests_on_the_plane_with_four_contacts(tmp_path):
