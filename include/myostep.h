@@ -335,6 +335,10 @@ typedef struct myo_env_desc {
   int32_t obj_bid, eps_ball_sid, obj_top_gid, obj_bot_gid;
   float pen_length, tar_length, target_axis[3];
   float w_pos_align, w_rot_align, w_r_act_reg, w_drop, w_r_bonus;
+  /* Geometries8EnvV0.reset (reorient_sar_v0.py:178-249): with randomize_shape every new episode draws the object's collision
+   * geom (obj_gid) as a capsule, ellipsoid, cylinder or box in one of two sizes and moves its top / bottom marker geoms
+   * accordingly, PER WORLD, through the batch's MYO_F_GEOM_TYPE_OVR / _SIZE_OVR / _POS_OVR buffers (which must be bound). */
+  int32_t randomize_shape, obj_gid;
 } myo_env_desc;
 
 typedef struct myo_env myo_env;

@@ -36,7 +36,8 @@ struct EnvParams {
   float min_height, max_rot, hip_period, target_x_vel, target_y_vel, target_rot[4], reset_noise, w_vel, w_done, w_cyclic, w_ref_rot, w_joint_angle;
   const float *xpos, *xquat, *xipos, *cvel, *actlen, *actvel, *actfrc;   // bound derived fields the walk observation reads
   // reorient env
-  int obj_bid, eps_sid, top_gid, bot_gid;
+  int obj_bid, eps_sid, top_gid, bot_gid, shape8, obj_gid;
+  int* gtype_ovr; float *gsize_ovr, *gpos_ovr;   // the batch's per-world geom override buffers (randomize_shape)
   float pen_length, tar_length, target_axis[3], w_pos_align, w_rot_align, w_r_act_reg, w_drop, w_r_bonus;
   const float *site_xpos, *geom_xpos;
   int* reset_mask;   // [nworld], library-owned: worlds reset by the last step (they need a full mj_forward)
@@ -126,6 +127,21 @@ __device__ void envResetWorld(const EnvParams& P, size_t w) {
       d[0] = (ax + 2.f * (qy * tz - qz * ty)) / P.tar_length; d[1] = (ay + 2.f * (qz * tx - qx * tz)) / P.tar_length; d[2] = (az + 2.f * (qx * ty - qy * tx)) / P.tar_length;
     }
     for (int k = 0; k < 3; k++) EF(MYO_E_TARGET, k) = d[k];
+    if (P.shape8) {
+      // Geometries8EnvV0.reset (reorient_sar_v0.py:178-245): geom_type uniform in {3, 4, 5, 6}, one of two sizes, the top /
+      // bottom markers at +-1.3 size[1] (capsule), +-size[1] (cylinder), +-size[2] (ellipsoid, box) on the object's axis
+      const int type = 3 + min(3, (int)(4.f * envUniform(P.seed, gw, ep, 5u, 0u))), big = envUniform(P.seed, gw, ep, 5u, 1u) < 0.5f ? 0 : 1;
+      float s0, s1, s2;
+      if (type == 3) { s0 = big ? 0.019f : 0.013f; s1 = s2 = big ? 0.040f : 0.025f; }
+      else if (type == 4) { s0 = big ? 0.019f : 0.011f; s1 = s2 = big ? 0.040f : 0.025f; }
+      else if (type == 5) { s0 = big ? 0.019f : 0.013f; s1 = s2 = big ? 0.040f : 0.025f; }
+      else { s0 = s1 = s2 = big ? 0.023f : 0.017f; }
+      const float z = type == 3 ? 1.3f * s1 : (type == 5 ? s1 : s2);
+      ST(P.gtype_ovr, P.obj_gid) = type;
+      ST(P.gsize_ovr, 3 * P.obj_gid) = s0; ST(P.gsize_ovr, 3 * P.obj_gid + 1) = s1; ST(P.gsize_ovr, 3 * P.obj_gid + 2) = s2;
+      ST(P.gpos_ovr, 3 * P.top_gid) = 0.f; ST(P.gpos_ovr, 3 * P.top_gid + 1) = 0.f; ST(P.gpos_ovr, 3 * P.top_gid + 2) = z;
+      ST(P.gpos_ovr, 3 * P.bot_gid) = 0.f; ST(P.gpos_ovr, 3 * P.bot_gid + 1) = 0.f; ST(P.gpos_ovr, 3 * P.bot_gid + 2) = -z;
+    }
   } else
   for (int k = 0; k < P.ntarget; k++) {
     float t;
@@ -418,6 +434,8 @@ int myo_env_create(myo_batch* b, const myo_env_desc* d, myo_env** out) {
   P.pose_thd = d->pose_thd; P.far_th = d->far_th; P.w_pose = d->w_pose; P.w_bonus = d->w_bonus; P.w_act_reg = d->w_act_reg; P.w_penalty = d->w_penalty;
   P.fat_F = d->fatigue_F; P.fat_R = d->fatigue_R; P.fat_r = d->fatigue_r;
   P.kind = d->kind; P.nbody = D.nbody;
+  P.shape8 = d->randomize_shape; P.obj_gid = d->obj_gid;
+  if (P.shape8 && (d->kind != MYO_ENV_REORIENT || d->obj_gid < 0 || d->obj_gid >= D.ngeom)) return myo_fail(MYO_ERR_ARG, "randomize_shape needs the reorient env and a valid obj_gid");
   P.obj_bid = d->obj_bid; P.eps_sid = d->eps_ball_sid; P.top_gid = d->obj_top_gid; P.bot_gid = d->obj_bot_gid; P.pen_length = d->pen_length; P.tar_length = d->tar_length;
   for (int k = 0; k < 3; k++) P.target_axis[k] = d->target_axis[k];
   P.w_pos_align = d->w_pos_align; P.w_rot_align = d->w_rot_align; P.w_r_act_reg = d->w_r_act_reg; P.w_drop = d->w_drop; P.w_r_bonus = d->w_r_bonus;
@@ -523,6 +541,11 @@ static int envReady(myo_env* e) {
     P.actlen = (const float*)F.p[MYO_F_ACTUATOR_LENGTH]; P.actvel = (const float*)F.p[MYO_F_ACTUATOR_VELOCITY]; P.actfrc = (const float*)F.p[MYO_F_ACTUATOR_FORCE];
     if (!P.xpos || !P.site_xpos || !P.geom_xpos || !P.actlen || !P.actvel || !P.actfrc)
       return myo_fail(MYO_ERR_UNBOUND, "the reorient env reads xpos, site_xpos, geom_xpos, actuator_length, actuator_velocity and actuator_force: bind them on the batch");
+    if (P.shape8) {
+      P.gtype_ovr = (int*)F.p[MYO_F_GEOM_TYPE_OVR]; P.gsize_ovr = (float*)F.p[MYO_F_GEOM_SIZE_OVR]; P.gpos_ovr = (float*)F.p[MYO_F_GEOM_POS_OVR];
+      if (!P.gtype_ovr || !P.gsize_ovr || !P.gpos_ovr)
+        return myo_fail(MYO_ERR_UNBOUND, "randomize_shape writes geom_type_ovr, geom_size_ovr and geom_pos_ovr: bind them on the batch");
+    }
   }
   if (cudaSetDevice(e->b->model->device) != cudaSuccess) return myo_fail(MYO_ERR_CUDA, "cudaSetDevice failed: libmyostep has no CPU fallback");
   return MYO_OK;

@@ -50,7 +50,7 @@ class EnvDesc(ctypes.Structure):
                 ("obj_bid", ctypes.c_int32), ("eps_ball_sid", ctypes.c_int32), ("obj_top_gid", ctypes.c_int32), ("obj_bot_gid", ctypes.c_int32),
                 ("pen_length", ctypes.c_float), ("tar_length", ctypes.c_float), ("target_axis", ctypes.c_float * 3),
                 ("w_pos_align", ctypes.c_float), ("w_rot_align", ctypes.c_float), ("w_r_act_reg", ctypes.c_float), ("w_drop", ctypes.c_float),
-                ("w_r_bonus", ctypes.c_float)]
+                ("w_r_bonus", ctypes.c_float), ("randomize_shape", ctypes.c_int32), ("obj_gid", ctypes.c_int32)]
 
 
 def _bind_protos(L):
@@ -160,23 +160,25 @@ def _quat2mat(q):
                      [2 * (x * z - w * y), 2 * (y * z + w * x), 1 - 2 * (x * x + y * y)]])
 
 
-def apply_reorient_setup(mj):
+def apply_reorient_setup(mj, geometries8=False):
     """ProprioceptiveEnvV0._setup edits the model before the first step: the object is 25 % heavier
-    (reorient_sar_v0.py:95).  Returns a copy of the host model to hand to put_model."""
+    (reorient_sar_v0.py:95); Geometries8EnvV0.reset then sets it to 1.2 at every reset (:247, the same value for every
+    episode, so it is a model edit here too).  Returns a copy of the host model to hand to put_model."""
     import copy
     m = copy.copy(mj)
     mass = np.array(mj.body_mass, dtype=np.float64, copy=True)
-    mass[list(map(str, mj.names_body)).index("Object")] *= 1.25
+    ob = list(map(str, mj.names_body)).index("Object")
+    mass[ob] = 1.2 if geometries8 else mass[ob] * 1.25
     m.body_mass = mass
     return m
 
 
-def reorient_config(mj, frame_skip=5, normalize_act=True, muscle_condition="", randomize_target=True, obs_keys=None, weights=None, horizon=50,
+def reorient_config(mj, frame_skip=5, normalize_act=True, muscle_condition="", randomize_target=True, randomize_shape=True, obs_keys=None, weights=None, horizon=50,
                     auto_reset=True, seed=0, world_offset=0, epl_id=-1, eip_id=-1):
     """ProprioceptiveEnvV0 (reorient_sar_v0.py:67-173; registered with frame_skip 5 and a 50-step horizon, myobase/__init__.py:639-649).
-    `randomize_target` draws a desired orientation per episode as Geometries8EnvV0.reset does (:251-257); the per-episode
-    change of the object's SHAPE (:207-249) needs per-world model tables and is not reproduced: the object keeps the
-    XML's geometry."""
+    `randomize_target` draws a desired orientation per episode as Geometries8EnvV0.reset does (:251-257); `randomize_shape`
+    draws the object's geometry per episode and per world (:178-249: capsule / ellipsoid / cylinder / box in two sizes, top and
+    bottom markers moved along) through the batch's geom override buffers."""
     nb, ng, ns = [str(x) for x in mj.names_body], [str(x) for x in mj.names_geom], [str(x) for x in mj.names_site]
     if obs_keys is None:
         obs_keys = ["hand_jnt", "obj_pos", "obj_vel", "obj_rot", "obj_des_rot", "obj_err_pos", "obj_err_rot", "mlen", "mvel", "mforce"]   # :97-108
@@ -199,6 +201,7 @@ def reorient_config(mj, frame_skip=5, normalize_act=True, muscle_condition="", r
     base.update(kind="reorient", obs_keys=obs_keys, reset_type="init", target_qposadr=np.zeros(3, np.int32), target_range=None,
                 target_value=des.astype(np.float32), target_type="generate" if randomize_target else "fixed",
                 obj_bid=nb.index("Object"), eps_ball_sid=ns.index("eps_ball"), top_gid=top, bot_gid=bot, pen_length=pen_length, tar_length=tar_length,
+                randomize_shape=bool(randomize_shape), obj_gid=ng.index("obj"),
                 target_axis=axis.astype(np.float32), reorient_weights=(w["pos_align"], w["rot_align"], w["act_reg"], w["drop"], w["bonus"]))
     return base
 
@@ -245,6 +248,7 @@ class FusedEnv:
             for i in range(3):
                 d.target_axis[i] = float(cfg["target_axis"][i])
             d.w_pos_align, d.w_rot_align, d.w_r_act_reg, d.w_drop, d.w_r_bonus = cfg["reorient_weights"]
+            d.randomize_shape, d.obj_gid = int(cfg.get("randomize_shape", False)), int(cfg.get("obj_gid", -1))
         if cfg.get("kind") == "walk":
             d.kind = 1
             d.foot_l_bid, d.foot_r_bid, d.pelvis_bid, d.torso_bid = cfg["foot_l"], cfg["foot_r"], cfg["pelvis"], cfg["torso"]

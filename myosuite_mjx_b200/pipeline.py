@@ -160,16 +160,18 @@ class WalkEnv(PipelineEnv):
 
 class ReorientEnv(WalkEnv):
     """myoHandReorient (reference: myosuite/envs/myo/myobase/reorient_sar_v0.py ProprioceptiveEnvV0 with the per-episode
-    target orientation of Geometries8EnvV0.reset) in the reset(rng) / step(State, action) shape.  The per-episode change of
-    the object's shape is not reproduced (envs.reorient_config)."""
+    target orientation AND object shape of Geometries8EnvV0.reset, drawn per world) in the reset(rng) / step(State, action)
+    shape."""
 
     def __init__(self, sys, n_frames=5, nworld=1, fields=None, **kw):
         from . import envs
         base_kw = {k: kw.pop(k) for k in ("device", "nconmax", "njmax", "backend") if k in kw}
         if not isinstance(sys, mjx.Model):
-            sys = envs.apply_reorient_setup(sys)
+            sys = envs.apply_reorient_setup(sys, geometries8=kw.get("randomize_shape", True))
         if fields is None:
             fields = mjx.CORE_FIELDS + envs.REORIENT_FIELDS
+            if kw.get("randomize_shape", True):
+                fields = fields + ("geom_type_ovr", "geom_size_ovr", "geom_pos_ovr")
         PipelineEnv.__init__(self, sys, n_frames=n_frames, nworld=nworld, fields=fields, **base_kw)
         self.cfg = envs.reorient_config(self.sys.mj, frame_skip=n_frames, **kw)
         self.env = envs.FusedEnv(self._data, self.cfg)

@@ -33,7 +33,7 @@ SPECS = {
                                                             normalize_act=True, pose_thd=0.7, reset_type="random", target_type="generate")),
     "myoLegWalk-v0": ("legs", "walk", 1000, dict(normalize_act=True, min_height=0.8, max_rot=0.8, hip_period=100, reset_type="init", target_x_vel=0.0,
                                                  target_y_vel=1.2, target_rot=None)),
-    # Geometries8EnvV0: target orientation per episode as registered; the object's per-episode shape change is not reproduced
+    # Geometries8EnvV0: target orientation and object shape drawn per episode and per world
     "myoHandReorient8-v0": ("hand_sar", "reorient", 50, dict(normalize_act=True, n_frames=5)),
 }
 for _k in range(10):   # ASL evaluation envs, one per numeral (__init__.py:383-396)

@@ -440,3 +440,44 @@ def test_length_range_simulation_on_device(models):
     ids, rng, spread = lengthrange.set_length_range(m)
     np.testing.assert_allclose(rng, want, rtol=1e-5, atol=1e-7)
     assert spread.max() < 1e-4
+
+
+def test_reorient8_draws_the_object_shape_per_world():
+    """myoHandReorient8-v0 (reference: reorient_sar_v0.py:176-260 Geometries8EnvV0.reset): every episode of every world draws
+    the object's collision geom -- capsule / ellipsoid / cylinder / box (geom_type 3..6), one of the two sizes of the reference's
+    tables, top and bottom markers moved along -- into the batch's per-world geom override buffers; physics then runs each
+    world with its own shape.  The reference draws from np_random: the distribution is reproduced, not the stream."""
+    import torch
+    from myosuite_mjx_b200 import registry
+    nw = 512
+    env = registry.make("myoHandReorient8-v0", nworld=nw)
+    d = env._data
+    g = [str(x) for x in env.sys.mj.names_geom]
+    obj, top, bot = g.index("obj"), g.index("top"), g.index("bot")
+    table = {3: ([0.013, 0.025, 0.025], [0.019, 0.040, 0.040]), 4: ([0.011, 0.025, 0.025], [0.019, 0.040, 0.040]),
+             5: ([0.013, 0.025, 0.025], [0.019, 0.040, 0.040]), 6: ([0.017, 0.017, 0.017], [0.023, 0.023, 0.023])}
+
+    def check():
+        t = d.geom_type_ovr[:, obj].cpu().numpy(); s = d.geom_size_ovr[:, obj].cpu().numpy()
+        tp = d.geom_pos_ovr[:, top].cpu().numpy(); bp = d.geom_pos_ovr[:, bot].cpu().numpy()
+        assert set(np.unique(t)) == {3, 4, 5, 6} and np.bincount(t)[3:].min() > nw // 8, np.bincount(t)
+        for w in range(nw):
+            opts = table[int(t[w])]
+            k = 0 if np.allclose(s[w], opts[0], atol=1e-7) else 1
+            assert np.allclose(s[w], opts[k], atol=1e-7), (w, t[w], s[w])
+            z = 1.3 * s[w][1] if t[w] == 3 else (s[w][1] if t[w] == 5 else s[w][2])
+            assert np.allclose(tp[w], [0, 0, z], atol=1e-7) and np.allclose(bp[w], [0, 0, -z], atol=1e-7)
+        others = torch.ones(len(g), dtype=torch.bool); others[obj] = False
+        assert (d.geom_type_ovr[:, others.to(d.geom_type_ovr.device)] == -1).all()      # only the object changes shape
+        return t.copy(), s.copy()
+    st = env.reset(7)
+    t0, s0 = check()
+    assert torch.isfinite(st.obs).all()
+    for _ in range(55):      # past the 50-step horizon: every world starts a new episode with a new draw
+        st = env.step(st, torch.rand((nw, env.action_size), device="cuda") * 2 - 1)
+    t1, s1 = check()
+    assert (t0 != t1).mean() > 0.5 and torch.isfinite(st.obs).all() and torch.isfinite(st.reward).all()
+    # the marker geoms follow the drawn shape in the kinematics: |top - bottom| = 2 z per world
+    span = (d.geom_xpos[:, top] - d.geom_xpos[:, bot]).norm(dim=1).cpu().numpy()
+    z = np.where(t1 == 3, 1.3 * s1[:, 1], np.where(t1 == 5, s1[:, 1], s1[:, 2]))
+    assert np.allclose(span, 2 * z, atol=2e-6)
