@@ -158,6 +158,12 @@ int myo_batch_create(const myo_model* m, int nworld, int nconmax, int njmax, myo
     void* q = nullptr;
     if (cudaMalloc(&q, (size_t)b->X.mpr_cap * sizeof(int2) + 256) != cudaSuccess || cudaMemset(q, 0, 256) != cudaSuccess) { myo_batch_destroy(b); return fail(MYO_ERR_CUDA, "cudaMalloc of the narrow-phase work list failed"); }
     b->owned.push_back(q); b->X.mpr_count = (int*)q; b->X.mpr_list = (int2*)((char*)q + 256);
+    b->X.dbg = nullptr;
+    if (getenv("MYO_NEWTON_TIMING")) {   // developer knob: per-tile clock sums of the solver's phases (myo_debug_timing)
+      void* t = nullptr;
+      const size_t tb = (size_t)((nworld + 31) / 32) * 32 * sizeof(long long);
+      if (cudaMalloc(&t, tb) == cudaSuccess && cudaMemset(t, 0, tb) == cudaSuccess) { b->owned.push_back(t); b->X.dbg = (long long*)t; }
+    }
   }
   // library-owned default state buffers (bind overrides them)
   for (int f : kStateFields) {
@@ -357,6 +363,12 @@ int myo_debug_layout(const myo_batch* b, int* out, int n) {
 int64_t myo_debug_scratch(myo_batch* b, float* host_out) {
   const int64_t n = (int64_t)((b->nworld + 31) / 32) * b->L.total * 32;
   if (host_out && (cudaDeviceSynchronize() != cudaSuccess || cudaMemcpy(host_out, b->scratch, n * sizeof(float), cudaMemcpyDeviceToHost) != cudaSuccess)) return -1;
+  return n;
+}
+int64_t myo_debug_timing(myo_batch* b, long long* host_out) {
+  const int64_t n = (int64_t)((b->nworld + 31) / 32) * 32;
+  if (!b->X.dbg) return 0;
+  if (host_out && (cudaDeviceSynchronize() != cudaSuccess || cudaMemcpy(host_out, b->X.dbg, n * sizeof(long long), cudaMemcpyDeviceToHost) != cudaSuccess)) return -1;
   return n;
 }
 int myo_kat_quat(int n, const float* qa, const float* qb, float* prod, float* mat, float* rotated, void* stream) {

@@ -128,6 +128,13 @@ struct SP {
   __device__ __forceinline__ float& operator[](int i) const { return p[i * SCR]; }
   __device__ __forceinline__ SP operator+(int k) const { SP r; r.p = p + k * SCR; return r; }
 };
+// Loads of the contact Jacobian blocks (conJ, conU: ~200 KB per tile and pass).  Measured (8192 MyoHand worlds): loading them
+// around L1 (ld.global.cg, -DSTREAM_J) is 1 % SLOWER than plain loads -- the blocks are re-read soon enough for L1 to help.
+#ifdef STREAM_J
+#define LDJ(ref) __ldcg(&(ref))
+#else
+#define LDJ(ref) (ref)
+#endif
 struct SPI {
   int* p;
   __device__ __forceinline__ int& operator[](int i) const { return p[i * SCR]; }
@@ -1320,9 +1327,9 @@ __device__ __noinline__ void baseMul(int slot, SP sm, Tm t, int ncon, SP x, SP o
     HOT
     for (; k + 1 < nv; k += 2) {
       const float x0 = x[k], x1 = x[k + 1];
-      a0 = fmaf(J0[k], x0, a0); a1 = fmaf(J0[k + 1], x1, a1); c0 = fmaf(J1[k], x0, c0); c1 = fmaf(J1[k + 1], x1, c1);
+      a0 = fmaf(LDJ(J0[k]), x0, a0); a1 = fmaf(LDJ(J0[k + 1]), x1, a1); c0 = fmaf(LDJ(J1[k]), x0, c0); c1 = fmaf(LDJ(J1[k + 1]), x1, c1);
     }
-    if (k < nv) { const float x0 = x[k]; a0 = fmaf(J0[k], x0, a0); c0 = fmaf(J1[k], x0, c0); }
+    if (k < nv) { const float x0 = x[k]; a0 = fmaf(LDJ(J0[k]), x0, a0); c0 = fmaf(LDJ(J1[k]), x0, c0); }
     out[b] = a0 + a1;
     if (b2 < nbr) out[b2] = c0 + c1;
   }
@@ -1426,10 +1433,10 @@ __device__ __noinline__ void constraintForce(int slot, SP sm, Tm t, int ncon, in
     for (; b + 1 < nbr; b += 2) {
       const float f0 = bf[b], f1 = bf[b + 1];
       auto Ja = Jk + b * nv; auto Jb = Jk + (b + 1) * nv;
-      a0 = fmaf(Ja[k0], f0, a0); a1 = fmaf(Ja[k1], f0, a1); a2 = fmaf(Ja[k2], f0, a2);
-      e0 = fmaf(Jb[k0], f1, e0); e1 = fmaf(Jb[k1], f1, e1); e2 = fmaf(Jb[k2], f1, e2);
+      a0 = fmaf(LDJ(Ja[k0]), f0, a0); a1 = fmaf(LDJ(Ja[k1]), f0, a1); a2 = fmaf(LDJ(Ja[k2]), f0, a2);
+      e0 = fmaf(LDJ(Jb[k0]), f1, e0); e1 = fmaf(LDJ(Jb[k1]), f1, e1); e2 = fmaf(LDJ(Jb[k2]), f1, e2);
     }
-    if (b < nbr) { const float f0 = bf[b]; auto Ja = Jk + b * nv; a0 = fmaf(Ja[k0], f0, a0); a1 = fmaf(Ja[k1], f0, a1); a2 = fmaf(Ja[k2], f0, a2); }
+    if (b < nbr) { const float f0 = bf[b]; auto Ja = Jk + b * nv; a0 = fmaf(LDJ(Ja[k0]), f0, a0); a1 = fmaf(LDJ(Ja[k1]), f0, a1); a2 = fmaf(LDJ(Ja[k2]), f0, a2); }
     out[k0] = res[0] + a0 + e0;
     if (kb + TEAM < nv) out[kb + TEAM] = res[1] + a1 + e1;
     if (kb + 2 * TEAM < nv) out[kb + 2 * TEAM] = res[2] + a2 + e2;

@@ -133,6 +133,7 @@ struct TileAux {
   int2* mpr_list;   // (world, survivor position) of the candidate pairs that need the convex narrow phase this pass
   int* mpr_count;   // entries appended so far (zeroed before every collision pass)
   int mpr_cap;
+  long long* dbg;   // developer timing of the solver phases ([tiles][32] clock64 sums; MYO_NEWTON_TIMING), else null
 };
 
 #endif  // MYO_DEVMODEL_H_

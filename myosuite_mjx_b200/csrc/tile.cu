@@ -574,13 +574,13 @@ __device__ __noinline__ void hessianAssemble(int slot, SP sm, Tm t, SP H, int nc
       if (nb == 3) {
         HOT
         for (int k = 0; k < nv; k++) {
-          const float jn = J[k], j1 = J[nv + k], j2 = J[2 * nv + k];
+          const float jn = LDJ(J[k]), j1 = LDJ(J[nv + k]), j2 = LDJ(J[2 * nv + k]);
           Uo[k] = fmaf(Wnt1, j2, fmaf(Wnt0, j1, Wnn * jn)); Uo[nv + k] = fmaf(Wnt0, jn, Wtt0 * j1); Uo[2 * nv + k] = fmaf(Wnt1, jn, Wtt1 * j2);
         }
       } else if (nb == 4) {
         HOT
         for (int k = 0; k < nv; k++) {
-          const float jn = J[k], j1 = J[nv + k], j2 = J[2 * nv + k], j3 = J[3 * nv + k];
+          const float jn = LDJ(J[k]), j1 = LDJ(J[nv + k]), j2 = LDJ(J[2 * nv + k]), j3 = LDJ(J[3 * nv + k]);
           Uo[k] = fmaf(Wnt2, j3, fmaf(Wnt1, j2, fmaf(Wnt0, j1, Wnn * jn)));
           Uo[nv + k] = fmaf(Wnt0, jn, Wtt0 * j1); Uo[2 * nv + k] = fmaf(Wnt1, jn, Wtt1 * j2); Uo[3 * nv + k] = fmaf(Wnt2, jn, Wtt2 * j3);
         }
@@ -607,7 +607,7 @@ __device__ __noinline__ void hessianAssemble(int slot, SP sm, Tm t, SP H, int nc
       for (int i = 0; i < nbase; i++) {
         float u[4], j[4];
 #pragma unroll
-        for (int a = 0; a < 4; a++) { u[a] = Ub[i * nv + ri[a]]; j[a] = Jb[i * nv + ci[a]]; }
+        for (int a = 0; a < 4; a++) { u[a] = LDJ(Ub[i * nv + ri[a]]); j[a] = LDJ(Jb[i * nv + ci[a]]); }
 #pragma unroll
         for (int a = 0; a < 4; a++)
 #pragma unroll
@@ -630,48 +630,62 @@ __device__ __noinline__ void hessianAssemble(int slot, SP sm, Tm t, SP H, int nc
 // walking its own flipped rows -- a few hundred instructions against the dense rebuild's ~10^5.
 __device__ __noinline__ void hessianUpdate(int slot, SP sm, Tm t, SP H, int nefc) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
-  const int nv = D.nv, nb = D.maxbase;
+  const int nv = D.nv, nb = D.maxbase, nw = t.nw;
   TFOR(i, TRI(nv)) H[i] = sm[L.Hsave + i];
+  // Each lane's flipped rows as a list (E_FORCE is free between the force evaluations): the lanes of a warp then take their
+  // i-th flipped row together -- walking all rows instead would run the update body once per row that flipped in ANY of the
+  // 32 worlds, with one or two lanes active each time.
+  // (built in order by per-warp chunks of the row range: count, prefix over the warps, write)
+  const int nrT = __reduce_max_sync(__activemask(), nefc) - D.neq, chunk = (max(nrT, 0) + nw - 1) / nw;
+  const int r0 = min(nefc, D.neq + t.tl * chunk), r1 = min(nefc, r0 + chunk);
+  int cnt = 0;
+  for (int r = r0; r < r1; r++) cnt += EFC(E_JV, r) != 0.f ? 1 : 0;
+  const TileScan sc = tileScan(t, cnt);
+  int at = sc.off;
+  for (int r = r0; r < r1; r++) if (EFC(E_JV, r) != 0.f) { EFC(E_FORCE, at) = __int_as_float(r); at++; }
+  const int nflip = sc.total;
   TSYNC();
-  if (t.tl == 0) {
-    for (int r = D.neq; r < nefc; r++) {
-      const float flip = EFC(E_JV, r);
-      if (flip == 0.f) continue;
-      const float s = flip * EFC(E_D, r);
-      const int d0 = EFCI(E_DESC0, r), type = d0 & 3, id = d0 >> 2;
-      const float coef = EFC(E_COEF, r);
-      if (type == ROW_LIMJ) { const int k = D.limj_dof[id]; H[TRI(k) + k] += s; }
-      else if (type == ROW_CON) {
-        const int bt = EFCI(E_DESC1, r), c = id / nb;
-        auto cr = sm + L.con + 12 * c;
-        const unsigned mlo = (unsigned)__float_as_int(cr[10]), mhi = (unsigned)__float_as_int(cr[11]);
-        auto Jn = sm + L.conJ + id * nv; auto Jt = sm + L.conJ + (bt >= 0 ? bt : id) * nv;
-        const float ct = bt >= 0 ? coef : 0.f;
-        for (int half = 0; half < 2; half++) {
-          unsigned wa = half ? mhi : mlo;
-          while (wa) {
-            const int a = 32 * half + __ffs((int)wa) - 1;
-            wa &= wa - 1u;
-            const float ja = s * fmaf(ct, Jt[a], Jn[a]);
-            auto Ha = H + TRI(a);
-            for (int h2 = 0; h2 <= half; h2++) {
-              unsigned wb = h2 ? mhi : mlo;
-              if (h2 == half) wb &= (2u << (a & 31)) - 1u;   // columns up to the diagonal
-              while (wb) {
-                const int b = 32 * h2 + __ffs((int)wb) - 1;
-                wb &= wb - 1u;
-                Ha[b] = fmaf(ja, fmaf(ct, Jt[b], Jn[b]), Ha[b]);
-              }
+  // every warp walks the lane's list but applies only the H rows it owns (a % nw == its index): no two warps touch one entry
+  for (int i = 0; i < nflip; i++) {
+    const int r = EFCI(E_FORCE, i);
+    const float s = EFC(E_JV, r) * EFC(E_D, r);
+    const int d0 = EFCI(E_DESC0, r), type = d0 & 3, id = d0 >> 2;
+    const float coef = EFC(E_COEF, r);
+    if (type == ROW_LIMJ) { const int k = D.limj_dof[id]; if (k % nw == t.tl) H[TRI(k) + k] += s; }
+    else if (type == ROW_CON) {
+      const int bt = EFCI(E_DESC1, r), c = id / nb;
+      auto cr = sm + L.con + 12 * c;
+      const unsigned mlo = (unsigned)__float_as_int(cr[10]), mhi = (unsigned)__float_as_int(cr[11]);
+      auto Jn = sm + L.conJ + id * nv; auto Jt = sm + L.conJ + (bt >= 0 ? bt : id) * nv;
+      const float ct = bt >= 0 ? coef : 0.f;
+      for (int half = 0; half < 2; half++) {
+        unsigned wa = half ? mhi : mlo;
+        while (wa) {
+          const int a = 32 * half + __ffs((int)wa) - 1;
+          wa &= wa - 1u;
+          if (a % nw != t.tl) continue;
+          const float ja = s * fmaf(ct, Jt[a], Jn[a]);
+          auto Ha = H + TRI(a);
+          for (int h2 = 0; h2 <= half; h2++) {
+            unsigned wb = h2 ? mhi : mlo;
+            if (h2 == half) wb &= (2u << (a & 31)) - 1u;   // columns up to the diagonal
+            while (wb) {
+              const int b = 32 * h2 + __ffs((int)wb) - 1;
+              wb &= wb - 1u;
+              Ha[b] = fmaf(ja, fmaf(ct, Jt[b], Jn[b]), Ha[b]);
             }
           }
         }
-      } else if (type == ROW_LIMT) {
-        const int tn = D.limt_ten[id], n0 = D.ten_nzstart[tn], n1 = D.ten_nzstart[tn + 1];
-        for (int a = n0; a < n1; a++)
-          for (int b = n0; b < n1; b++) {
-            const int da = D.nz_dof[a], db = D.nz_dof[b];
-            if (da >= db) H[TRI(da) + db] += s * sm[L.tenJ + a] * sm[L.tenJ + b];   // coef^2 = 1
-          }
+      }
+    } else if (type == ROW_LIMT) {
+      const int tn = D.limt_ten[id], n0 = D.ten_nzstart[tn], n1 = D.ten_nzstart[tn + 1];
+      for (int a = n0; a < n1; a++) {
+        const int da = D.nz_dof[a];
+        if (da % nw != t.tl) continue;
+        for (int b = n0; b < n1; b++) {
+          const int db = D.nz_dof[b];
+          if (da >= db) H[TRI(da) + db] += s * sm[L.tenJ + a] * sm[L.tenJ + b];   // coef^2 = 1
+        }
       }
     }
   }
@@ -750,8 +764,11 @@ template <int K> __device__ __forceinline__ void lsEvalTile(int slot, SP sm, Tm 
 
 struct NewtonMem { SP H, Hd, qacc, Ma, grad, search, Mv, tmp; };
 // mj_solNewton for the 32 worlds of the tile in lock step; returns the lane's iteration count
+// developer timing (MYO_NEWTON_TIMING): thread 0 of the tile adds the clocks since the last mark to slot k of its tile's row
+#define TICK(k) do { if (dbg && threadIdx.x == 0) { const long long now_ = clock64(); dbg[blockIdx.x * 32 + (k)] += now_ - tlast; tlast = now_; } } while (0)
 __device__ __noinline__ int newtonTile(int slot, SP sm, Tm t, const NewtonMem& M, unsigned lmask, int ncon, int nconT, int nefc, int* status) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
+  long long* dbg = tP[slot].X.dbg; long long tlast = dbg ? clock64() : 0;
   const int nv = D.nv, nw = t.nw;
   SP qacc = M.qacc, Ma = M.Ma, grad = M.grad, search = M.search, Mv = M.Mv, tmp = M.tmp;
   auto smooth = sm + L.smooth; auto qas = sm + L.qacc_smooth; auto warm = sm + L.warm;
@@ -780,6 +797,7 @@ __device__ __noinline__ int newtonTile(int slot, SP sm, Tm t, const NewtonMem& M
     gauss = TSUM(g);
     cost = gauss + residualCost(slot, sm, t, ncon, nefc, qacc);
   }
+  TICK(1);
   int iter = 0, pass = 0;   // pass: Newton passes of the tile so far (tile-uniform)
   bool active = nefc > 0;
   const int lsmax = D.ls_iterations;
@@ -797,11 +815,15 @@ __device__ __noinline__ int newtonTile(int slot, SP sm, Tm t, const NewtonMem& M
     // O(gr) terms and bottoms out near eps * gr, after which further iterations only chase rounding noise.
     if (active && iter > 0 && (scale * gn < D.tolerance || gn < GRAD_NOISE * gr)) active = false;
     if (active && iter >= D.iterations) { *status |= MYO_WORLD_SOLVER_MAXITER; active = false; }
+    TICK(2);
     if (!__ballot_sync(lmask, active)) break;   // the tile is done when its slowest world is
-    if (pass == 0) hessianAssemble(slot, sm, t, M.H, ncon, nconT, nefc); else hessianUpdate(slot, sm, t, M.H, nefc);
+    if (pass == 0) { hessianAssemble(slot, sm, t, M.H, ncon, nconT, nefc); TICK(3); } else { hessianUpdate(slot, sm, t, M.H, nefc); TICK(4); }
     choleskyTile(nv, M.H, M.Hd, t);
+    TICK(5);
     pass++;
+    if (dbg && threadIdx.x == 0) dbg[blockIdx.x * 32 + 11] += 1;
     cholSolveTile(nv, M.H, M.Hd, search, tmp, t);
+    TICK(6);
     float sn = 0.f;
     TFOR(k, nv) { const float s = -search[k]; search[k] = s; sn = fmaf(s, s, sn); }
     sn = sqrtf(TSUM(sn));
@@ -815,6 +837,7 @@ __device__ __noinline__ int newtonTile(int slot, SP sm, Tm t, const NewtonMem& M
     float g12[2] = {0.f, 0.f};
     TFOR(k, nv) { g12[0] = fmaf(search[k], Ma[k] - smooth[k], g12[0]); g12[1] = fmaf(0.5f * search[k], Mv[k], g12[1]); }
     tileSumN<2>(t, g12);   // its barriers also publish E_JV
+    TICK(7);
     const float qg[3] = {gauss, g12[0], g12[1]};
     const float gtol = D.tolerance * D.ls_tolerance * sn / scale;
     int lsiter = 0;
@@ -859,6 +882,7 @@ __device__ __noinline__ int newtonTile(int slot, SP sm, Tm t, const NewtonMem& M
         else p1 = lo.cost < hi.cost ? lo : hi;
       }
     }
+    TICK(8);
     const float alpha = p1.alpha;
     if (active && alpha == 0.f) active = false;
     if (active) TFOR(k, nv) { qacc[k] = fmaf(alpha, search[k], qacc[k]); Ma[k] = fmaf(alpha, Mv[k], Ma[k]); }
@@ -884,8 +908,10 @@ __device__ __noinline__ int newtonTile(int slot, SP sm, Tm t, const NewtonMem& M
       cost = newcost;
       if (improvement < D.tolerance) active = false;
     }
+    TICK(9);
   }
   constraintForce(slot, sm, t, ncon, nefc, sm + L.qfrc_con);
+  TICK(10);
   return iter;
 }
 
@@ -908,7 +934,9 @@ __global__ void __launch_bounds__(32 * MAXW, MINB_NEWTON) newtonKernel(int slot,
   const int ncon = __float_as_int(sm[L.counts]);
   const int nconT = __reduce_max_sync(lmask, ncon);
   if (t.tl == 0) sBad[lane] = 0;
+  long long* dbg = tP[slot].X.dbg; long long tlast = dbg ? clock64() : 0;
   int nefc = makeConstraintTile(slot, sm, t, ncon, nconT, &status);
+  TICK(0);
   const int nefcT = __reduce_max_sync(lmask, nefc);
   int niter = 0;
   if (nefcT == 0) {   // tile-uniform
