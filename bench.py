@@ -155,7 +155,7 @@ def run_reference(args, rank, world):
 
 
 WORKLOAD = "MyoHand ({model}.xml, play.py:8) random-ctrl rollout, {nworld} worlds/GPU, dt 0.002, Newton, full mjData written every step"
-KERNELS = "one myo_step = kin, tendon | inertia | collide (+ collideMpr, collideCompact), velact, newton, conout | finish (csrc/tile.cu, lane = world)"
+KERNELS = "one myo_step = kin, tendon | inertia | collide (+ collideMpr, collideCompact, makecon), velact, newton | conout, finish: 11 launches + 2 empty ordering launches (csrc/tile.cu, lane = world)"
 
 
 def main():
@@ -235,32 +235,28 @@ def main():
     launches = lib.lib().myo_launch_count() - launches0
     value = nw * world * args.steps * args.nsub / (total_ms * 1e-3)
 
-    # ---- steady state: the same rollout once the hand has clenched (a short driver run times the contact-poor first steps)
-    steady = None
-    if not args.no_steady:
-        while step_no[0] < STEADY_AFTER:
-            one_step()
-        after = step_no[0]
-        s_ms, s_kernel_ms = timed(STEADY_STEPS)
-        fields = d.fields()
-        steady = {"value": nw * world * STEADY_STEPS * args.nsub / (s_ms * 1e-3), "unit": "env-steps/s", "ms_per_step": s_ms / STEADY_STEPS,
-                  "kernel_ms": s_kernel_ms, "after_steps": after, "steps": STEADY_STEPS,
-                  "ncon_mean": float(d.ncon.float().mean()) if "ncon" in fields else None,
-                  "nefc_mean": float(d.nefc.float().mean()) if "nefc" in fields else None}
-
     # ---- end to end through the C ABI with pinned host buffers, every step: H2D of the step's input (ctrl; the state is
     # carried on the device from the previous step, as in the reference's env.step(a) loop), step, D2H of the new state.
     # Host buffers in the ABI layout [k][nworld].  The full mjData stays on the device (a host caller receives the state).
+    # Runs right after the device-timed leg, on the same rollout (same ctrl sequence), so `e2e` and `value` see the same phase.
     hq = torch.empty((m.nq, nw), dtype=torch.float32).pin_memory(); hv = torch.zeros((m.nv, nw), dtype=torch.float32).pin_memory()
-    ha = torch.zeros((m.na, nw), dtype=torch.float32).pin_memory(); hc = torch.rand((m.nu, nw), dtype=torch.float32).pin_memory()
+    ha = torch.zeros((m.na, nw), dtype=torch.float32).pin_memory()
     import ctypes
     L = lib.lib()
     vp = ctypes.c_void_p
     e2e_steps = max(10, min(250, args.steps // 4))
 
+    # the policy's outputs for the leg, one pinned [nu][nworld] buffer per control frame (made before the timed region)
+    frame0 = step_no[0] // FRAME_SKIP
+    nframes = (step_no[0] + e2e_steps + 3) // FRAME_SKIP - frame0 + 1
+    hcs = [torch.from_numpy(np.ascontiguousarray(partition.ctrl_hash_np(m.nu, range(w0, w0 + nw), SEED, frame0 + f).T.astype(np.float32))).pin_memory()
+           for f in range(nframes)]
+
     def host_step():
+        hc = hcs[step_no[0] // FRAME_SKIP - frame0]
         lib.check(L.myo_step_host(d._h, args.nsub, None, None, None, vp(hc.data_ptr()),
                                   vp(hq.data_ptr()), vp(hv.data_ptr()), vp(ha.data_ptr()), vp(stream.cuda_stream)))
+        step_no[0] += 1
     for _ in range(3):
         host_step()
     torch.cuda.synchronize()
@@ -278,6 +274,19 @@ def main():
     e2e_value = nw * world * e2e_steps * args.nsub / (float(te.item()) * 1e-3)
     h2d = nw * m.nu * 4
     d2h = nw * (m.nq + m.nv + m.na) * 4
+
+    # ---- steady state: the same rollout once the hand has clenched (a short driver run times the contact-poor first steps)
+    steady = None
+    if not args.no_steady:
+        while step_no[0] < STEADY_AFTER:
+            one_step()
+        after = step_no[0]
+        s_ms, s_kernel_ms = timed(STEADY_STEPS)
+        fields = d.fields()
+        steady = {"value": nw * world * STEADY_STEPS * args.nsub / (s_ms * 1e-3), "unit": "env-steps/s", "ms_per_step": s_ms / STEADY_STEPS,
+                  "kernel_ms": s_kernel_ms, "after_steps": after, "steps": STEADY_STEPS,
+                  "ncon_mean": float(d.ncon.float().mean()) if "ncon" in fields else None,
+                  "nefc_mean": float(d.nefc.float().mean()) if "nefc" in fields else None}
 
     # ---- optional episode statistics all-reduce: the only collective, off the step path
     stats = partition.all_reduce_stats(partition.episode_stats(d.status, d.qvel))

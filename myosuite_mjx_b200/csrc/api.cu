@@ -162,7 +162,9 @@ int myo_batch_create(const myo_model* m, int nworld, int nconmax, int njmax, myo
     if (getenv("MYO_NEWTON_TIMING")) {   // developer knob: per-tile clock sums of the solver's phases (myo_debug_timing)
       void* t = nullptr;
       const size_t tb = (size_t)((nworld + 31) / 32) * 32 * sizeof(long long);
-      if (cudaMalloc(&t, tb) == cudaSuccess && cudaMemset(t, 0, tb) == cudaSuccess) { b->owned.push_back(t); b->X.dbg = (long long*)t; }
+      if (cudaMalloc(&t, tb + 64 * sizeof(long long)) == cudaSuccess && cudaMemset(t, 0, tb + 64 * sizeof(long long)) == cudaSuccess) {
+        b->owned.push_back(t); b->X.dbg = (long long*)t; b->X.tl_off = (int)(tb / sizeof(long long));
+      }
     }
   }
   // library-owned default state buffers (bind overrides them)
@@ -179,7 +181,7 @@ void myo_batch_destroy(myo_batch* b) {
   if (!b) return;
   cudaSetDevice(b->model->device);
   for (void* p : b->owned) cudaFree(p);
-  for (int i = 0; i < 2; i++) if (b->side[i]) { cudaStreamSynchronize((cudaStream_t)b->side[i]); cudaStreamDestroy((cudaStream_t)b->side[i]); }
+  for (int i = 0; i < 4; i++) if (b->side[i]) { cudaStreamSynchronize((cudaStream_t)b->side[i]); cudaStreamDestroy((cudaStream_t)b->side[i]); }
   for (int i = 0; i < 6; i++) if (b->ev[i]) cudaEventDestroy((cudaEvent_t)b->ev[i]);
   releaseSlot(b->slot);
   delete b;
@@ -240,7 +242,14 @@ static int launchPhases(myo_batch* b, int nsub, int forward_only, const int32_t*
   }
   static const bool concurrent = !(getenv("MYO_CONCURRENT") && atoi(getenv("MYO_CONCURRENT")) == 0);   // developer knob
   if (concurrent && !b->side[0]) {
-    for (int i = 0; i < 2; i++) { cudaStream_t cs; if (cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking) != cudaSuccess) return fail(MYO_ERR_CUDA, "side stream creation failed"); b->side[i] = cs; }
+    // side streams: 0 = collision chain + constraint rows (the longest branch: highest priority, so its CTAs get the first
+    // free slots), 1 = tendon -> velact, 2 = inertia, 3 = contact / constraint records (lowest priority: they only have to
+    // be out by the end of the step and must not take slots from the solver)
+    int least = 0, greatest = 0;
+    cudaDeviceGetStreamPriorityRange(&least, &greatest);
+    static const bool prio = !(getenv("MYO_PRIORITY") && atoi(getenv("MYO_PRIORITY")) == 0);   // developer knob
+    const int pr[4] = {prio ? greatest : least, prio ? std::min(least, greatest + 1) : least, prio ? std::min(least, greatest + 2) : least, least};
+    for (int i = 0; i < 4; i++) { cudaStream_t cs; if (cudaStreamCreateWithPriority(&cs, cudaStreamNonBlocking, pr[i]) != cudaSuccess) return fail(MYO_ERR_CUDA, "side stream creation failed"); b->side[i] = cs; }
     for (int i = 0; i < 6; i++) { cudaEvent_t e; if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess) return fail(MYO_ERR_CUDA, "event creation failed"); b->ev[i] = e; }
   }
   const bool posvel = forward_only == 2;
@@ -262,7 +271,6 @@ static int launchPhases(myo_batch* b, int nsub, int forward_only, const int32_t*
   // mj_collision = broad phase + closed-form pairs, the listed convex pairs one per lane, ordered compaction
   auto collide = [&](int fslot) {
     bool r = true;
-    if (b->D.npair > 0) r &= cudaMemsetAsync(b->X.mpr_count, 0, sizeof(int), (cudaStream_t)cur) == cudaSuccess;
     r &= tile(MYO_K_COLLIDE, fslot, 0) == 0;
     if (b->D.npair > 0) {
       if (b->D.nmprpair > 0 || b->F.p[MYO_F_GEOM_TYPE_OVR]) r &= tile(MYO_K_COLLIDE_MPR, fslot, 0) == 0;
@@ -277,37 +285,61 @@ static int launchPhases(myo_batch* b, int nsub, int forward_only, const int32_t*
     const bool first = sub == 0, last = sub == nloop - 1;
     const int fslot = last ? slot : MYO_PARAM_SLOTS;   // slot MYO_PARAM_SLOTS: no field bound, "materialise nothing"
     ok &= tile(MYO_K_KIN, fslot, (first ? (do_reset ? MYO_KIN_RESET : MYO_KIN_LOAD) : 0) | (forward_only ? 0 : MYO_KIN_CHECK)) == 0; STOP_HERE();
+    // mj_makeConstraint needs the contacts and qvel only -- unless the model has tendon limits (tendon length / velocity)
+    const bool makecon_early = b->D.nlimt == 0;
+    const bool conout = last && b->conout;
     if (concurrent && !posvel && debug_stop < 0) {
-      // fork: tendon and inertia on the side streams, collide on the caller's; join before velact
+      // fork after kin: collision chain (+ constraint rows, + records out) | tendon -> velact | inertia; join before the solver
       auto S = [&](int i) { return (cudaStream_t)b->side[i]; };
       auto E = [&](int i) { return (cudaEvent_t)b->ev[i]; };
-      ok &= cudaEventRecord(E(0), (cudaStream_t)stream) == cudaSuccess;
-      ok &= cudaStreamWaitEvent(S(0), E(0), 0) == cudaSuccess && cudaStreamWaitEvent(S(1), E(0), 0) == cudaSuccess;
-      cur = b->side[0]; ok &= tile(MYO_K_TENDON, fslot, 0) == 0;
-      cur = b->side[1]; ok &= tile(MYO_K_INERTIA, fslot, forward_only ? 0 : 1) == 0;
-      cur = stream;     ok &= collide(fslot);
-      ok &= cudaEventRecord(E(1), S(0)) == cudaSuccess && cudaEventRecord(E(2), S(1)) == cudaSuccess;
-      ok &= cudaStreamWaitEvent((cudaStream_t)stream, E(1), 0) == cudaSuccess && cudaStreamWaitEvent((cudaStream_t)stream, E(2), 0) == cudaSuccess;
-    } else {
-      ok &= tile(MYO_K_TENDON, fslot, 0) == 0; STOP_HERE();
-      if (!posvel) {
-        ok &= tile(MYO_K_INERTIA, fslot, forward_only ? 0 : 1) == 0; STOP_HERE();
-        ok &= collide(fslot); STOP_HERE();
+      const cudaStream_t main = (cudaStream_t)stream;
+      ok &= cudaEventRecord(E(0), main) == cudaSuccess;
+      for (int i = 0; i < 3; i++) ok &= cudaStreamWaitEvent(S(i), E(0), 0) == cudaSuccess;
+      static const bool conout_late = getenv("MYO_CONOUT_LATE") && atoi(getenv("MYO_CONOUT_LATE"));   // developer knob
+      auto rows = [&](cudaStream_t on) {   // on the stream `cur` = `on`
+        ok &= tile(MYO_K_MAKECON, fslot, 0) == 0;
+        if (conout && !conout_late) {
+          ok &= cudaEventRecord(E(3), on) == cudaSuccess && cudaStreamWaitEvent(S(3), E(3), 0) == cudaSuccess;
+          void* keep = cur; cur = b->side[3]; ok &= tile(MYO_K_CONOUT, fslot, 0) == 0; cur = keep;
+          ok &= cudaEventRecord(E(4), S(3)) == cudaSuccess;
+        }
+      };
+      cur = b->side[0]; ok &= collide(fslot);
+      if (makecon_early) rows(S(0));
+      ok &= cudaEventRecord(E(1), S(0)) == cudaSuccess;
+      static const int ndelay = getenv("MYO_DELAY") ? atoi(getenv("MYO_DELAY")) : 1;   // developer knob
+      for (int i = 0; i < ndelay; i++) { g_launches += 2; ok &= myo_nop_launch(b->side[1]) == 0 && myo_nop_launch(b->side[2]) == 0; }
+      cur = b->side[1]; ok &= tile(MYO_K_TENDON, fslot, 0) == 0;
+      cur = b->side[2]; ok &= tile(MYO_K_INERTIA, fslot, forward_only ? 0 : 1) == 0;
+      ok &= cudaEventRecord(E(2), S(2)) == cudaSuccess && cudaStreamWaitEvent(S(1), E(2), 0) == cudaSuccess;
+      cur = b->side[1]; ok &= tile(MYO_K_VELACT, fslot, 0) == 0;
+      ok &= cudaEventRecord(E(5), S(1)) == cudaSuccess;
+      cur = stream;
+      ok &= cudaStreamWaitEvent(main, E(1), 0) == cudaSuccess && cudaStreamWaitEvent(main, E(5), 0) == cudaSuccess;
+      if (!makecon_early) rows(main);
+      ok &= tile(MYO_K_NEWTON, fslot, (forward_only ? 0 : 1) | (b->D.nv << 8)) == 0;
+      if (conout && conout_late) {
+        ok &= cudaEventRecord(E(3), main) == cudaSuccess && cudaStreamWaitEvent(S(3), E(3), 0) == cudaSuccess;
+        cur = b->side[3]; ok &= tile(MYO_K_CONOUT, fslot, 0) == 0; cur = stream;
+        ok &= cudaEventRecord(E(4), S(3)) == cudaSuccess;
       }
+      ok &= tile(MYO_K_FINISH, fslot, (forward_only ? 0 : MYO_FIN_EULER) | (last && (!forward_only || do_reset) ? MYO_FIN_STATE : 0) |
+                                          (last ? MYO_FIN_WARM | MYO_FIN_ACC : 0)) == 0;
+      if (conout) ok &= cudaStreamWaitEvent(main, E(4), 0) == cudaSuccess;
+      continue;
+    }
+    ok &= tile(MYO_K_TENDON, fslot, 0) == 0; STOP_HERE();
+    if (!posvel) {
+      ok &= tile(MYO_K_INERTIA, fslot, forward_only ? 0 : 1) == 0; STOP_HERE();
+      ok &= collide(fslot); STOP_HERE();
     }
     ok &= tile(MYO_K_VELACT, fslot, posvel ? 1 : 0) == 0; STOP_HERE();
     if (posvel) break;
-    ok &= tile(MYO_K_NEWTON, fslot, (forward_only ? 0 : 1) | (b->D.nv << 8)) == 0;
-    STOP_HERE();
-    const bool forkout = concurrent && last && b->conout && debug_stop < 0;
-    if (forkout) {   // the contact / constraint records go out on a side stream under mj_Euler and the state outputs
-      ok &= cudaEventRecord((cudaEvent_t)b->ev[3], (cudaStream_t)stream) == cudaSuccess && cudaStreamWaitEvent((cudaStream_t)b->side[0], (cudaEvent_t)b->ev[3], 0) == cudaSuccess;
-      cur = b->side[0]; ok &= tile(MYO_K_CONOUT, fslot, 0) == 0; cur = stream;
-      ok &= cudaEventRecord((cudaEvent_t)b->ev[4], (cudaStream_t)b->side[0]) == cudaSuccess;
-    } else if (last && b->conout) { ok &= tile(MYO_K_CONOUT, fslot, 0) == 0; STOP_HERE(); }
+    ok &= tile(MYO_K_MAKECON, fslot, 0) == 0; STOP_HERE();
+    if (conout) { ok &= tile(MYO_K_CONOUT, fslot, 0) == 0; STOP_HERE(); }
+    ok &= tile(MYO_K_NEWTON, fslot, (forward_only ? 0 : 1) | (b->D.nv << 8)) == 0; STOP_HERE();
     ok &= tile(MYO_K_FINISH, fslot, (forward_only ? 0 : MYO_FIN_EULER) | (last && (!forward_only || do_reset) ? MYO_FIN_STATE : 0) |
                                         (last ? MYO_FIN_WARM | MYO_FIN_ACC : 0)) == 0;
-    if (forkout) ok &= cudaStreamWaitEvent((cudaStream_t)stream, (cudaEvent_t)b->ev[4], 0) == cudaSuccess;
   }
   if (!ok) return fail(MYO_ERR_CUDA, std::string("kernel launch failed: ") + cudaGetErrorString(cudaGetLastError()));
   return MYO_OK;
@@ -370,6 +402,16 @@ int64_t myo_debug_timing(myo_batch* b, long long* host_out) {
   if (!b->X.dbg) return 0;
   if (host_out && (cudaDeviceSynchronize() != cudaSuccess || cudaMemcpy(host_out, b->X.dbg, n * sizeof(long long), cudaMemcpyDeviceToHost) != cudaSuccess)) return -1;
   return n;
+}
+// developer: per-kernel [start, end] globaltimer marks since the last call (32 kernels x 2); the call re-arms them
+int myo_debug_timeline(myo_batch* b, unsigned long long* host_out) {
+  if (!b->X.dbg) return 0;
+  unsigned long long* p = (unsigned long long*)b->X.dbg + b->X.tl_off;
+  if (cudaDeviceSynchronize() != cudaSuccess) return -1;
+  if (host_out && cudaMemcpy(host_out, p, 64 * sizeof(long long), cudaMemcpyDeviceToHost) != cudaSuccess) return -1;
+  unsigned long long arm[64];
+  for (int i = 0; i < 64; i++) arm[i] = (i & 1) ? 0ull : ~0ull;
+  return cudaMemcpy(p, arm, sizeof(arm), cudaMemcpyHostToDevice) == cudaSuccess ? 64 : -1;
 }
 int myo_kat_quat(int n, const float* qa, const float* qb, float* prod, float* mat, float* rotated, void* stream) {
   if (n <= 0 || !qa || !qb || !prod || !mat || !rotated) return fail(MYO_ERR_ARG, "bad argument");

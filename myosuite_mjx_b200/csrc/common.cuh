@@ -765,15 +765,12 @@ __device__ __noinline__ void inertia(int slot, int fslot, SP sm, Tm t, World W) 
 }
 
 // ------------------------------------------------------------------------------------------ mj_fwdVelocity
-__device__ __noinline__ void velocity(int slot, int fslot, SP sm, Tm t, World W) {
+// The part that needs only the kinematics and qvel (body velocities, cdof_dot, mj_rne's bias force): it runs in
+// inertiaKernel, beside the tendon stage; the tendon / passive part below follows the tendon stage in velactKernel.
+__device__ __noinline__ void velocityBody(int slot, int fslot, SP sm, Tm t, World W) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L; const FieldPtrs& F = tP[fslot].F;
   const int nv = D.nv;
   auto qvel = sm + L.qvel;
-  TFOR(k, D.nten) {
-    float acc = 0.f;
-    for (int n = D.ten_nzstart[k]; n < D.ten_nzstart[k + 1]; n++) acc = fmaf(sm[L.tenJ + n], qvel[D.nz_dof[n]], acc);
-    sm[L.tenvel + k] = acc;
-  }
   // body velocities: sum of the ancestor dof motions (all expressed about the tree's centre of mass)
   TFOR(f, D.nframe) {
     float v[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
@@ -822,8 +819,7 @@ __device__ __noinline__ void velocity(int slot, int fslot, SP sm, Tm t, World W)
     for (int k = 0; k < 6; k++) sm[L.cacc + 6 * f + k] = Ia[k] + cf[k];   // cacc now holds the body force cfrc
   }
   TSYNC();
-  const bool passive_on = !(D.disableflags & DSBL_PASSIVE);
-  void* osp = F.p[MYO_F_QFRC_SPRING]; void* odm = F.p[MYO_F_QFRC_DAMPER]; void* ops = F.p[MYO_F_QFRC_PASSIVE]; void* obi = F.p[MYO_F_QFRC_BIAS];
+  void* obi = F.p[MYO_F_QFRC_BIAS];
   TFOR(i, nv) {
     const int f = D.dof_frame[i];
     float acc[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
@@ -833,6 +829,27 @@ __device__ __noinline__ void velocity(int slot, int fslot, SP sm, Tm t, World W)
     auto cd = sm + L.cdof + 6 * i;
     const float bias = cd[0] * acc[0] + cd[1] * acc[1] + cd[2] * acc[2] + cd[3] * acc[3] + cd[4] * acc[4] + cd[5] * acc[5];
     sm[L.bias + i] = bias;
+    if (obi) OUTF(obi, i) = bias;
+  }
+  void* o;
+  if ((o = F.p[MYO_F_CDOF_DOT])) TFOR(i, 6 * nv) OUTF(o, i) = sm[L.cdof_dot + i];
+  if ((o = F.p[MYO_F_CVEL])) TFOR(i, 6 * D.nbody) OUTF(o, i) = sm[L.cvel + 6 * D.body_frame[i / 6] + i % 6];
+  TSYNC();
+}
+// tendon velocities and mj_passive
+__device__ __noinline__ void velocityTendon(int slot, int fslot, SP sm, Tm t, World W) {
+  const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L; const FieldPtrs& F = tP[fslot].F;
+  const int nv = D.nv;
+  auto qvel = sm + L.qvel;
+  TFOR(k, D.nten) {
+    float acc = 0.f;
+    for (int n = D.ten_nzstart[k]; n < D.ten_nzstart[k + 1]; n++) acc = fmaf(sm[L.tenJ + n], qvel[D.nz_dof[n]], acc);
+    sm[L.tenvel + k] = acc;
+  }
+  if (D.any_tendon_passive) TSYNC();
+  const bool passive_on = !(D.disableflags & DSBL_PASSIVE);
+  void* osp = F.p[MYO_F_QFRC_SPRING]; void* odm = F.p[MYO_F_QFRC_DAMPER]; void* ops = F.p[MYO_F_QFRC_PASSIVE];
+  TFOR(i, nv) {
     float spring = 0.f, damper = 0.f;
     if (passive_on) {
       const int j = D.dof_jnt[i];
@@ -855,12 +872,9 @@ __device__ __noinline__ void velocity(int slot, int fslot, SP sm, Tm t, World W)
     if (osp) OUTF(osp, i) = spring;
     if (odm) OUTF(odm, i) = damper;
     if (ops) OUTF(ops, i) = spring + damper;
-    if (obi) OUTF(obi, i) = bias;
   }
   void* o;
   if ((o = F.p[MYO_F_TEN_VELOCITY])) TFOR(k, D.nten) OUTF(o, k) = sm[L.tenvel + k];
-  if ((o = F.p[MYO_F_CDOF_DOT])) TFOR(i, 6 * nv) OUTF(o, i) = sm[L.cdof_dot + i];
-  if ((o = F.p[MYO_F_CVEL])) TFOR(i, 6 * D.nbody) OUTF(o, i) = sm[L.cvel + 6 * D.body_frame[i / 6] + i % 6];
   TSYNC();
 }
 
@@ -1030,7 +1044,9 @@ struct Sup { d3 v, a, b; };
 __device__ __noinline__ Sup mprSup(const Shape& A, const Shape& B, d3 d) {
   Sup s; s.a = supportPt(A, d * -1.0); s.b = supportPt(B, d); s.v = s.b - s.a; return s;
 }
-__device__ __noinline__ bool mprPenetration(const Shape& A, const Shape& B, double tol, int maxit, double* depth, d3* nrm, d3* pos) {
+// portal_only: stop once a portal exists (true) -- every early "no intersection" exit lies before that point or in the first
+// refinement steps, so this is the cheap filter collideMprKernel compacts its work list with
+__device__ __noinline__ bool mprPenetration(const Shape& A, const Shape& B, double tol, int maxit, double* depth, d3* nrm, d3* pos, bool portal_only) {
   d3 v0 = B.pos - A.pos;
   if (norm3(v0) < 1e-12) v0 = mkd(1e-5, 0.0, 0.0);
   d3 dir = unit3(v0 * -1.0);
@@ -1039,6 +1055,7 @@ __device__ __noinline__ bool mprPenetration(const Shape& A, const Shape& B, doub
   dir = cross(s1.v, v0);
   if (norm3(dir) < 1e-12 * fmax(1.0, norm3(s1.v) * norm3(v0))) {
     const d3 n = unit3(s1.v - v0);
+    if (portal_only) return true;
     *depth = dot(s1.v, n); *nrm = n * -1.0; *pos = (s1.a + s1.b) * 0.5;
     return true;
   }
@@ -1057,6 +1074,7 @@ __device__ __noinline__ bool mprPenetration(const Shape& A, const Shape& B, doub
     if (dot(cross(s3.v, s2.v), v0) < 0.0) { s1 = s3; dir = unit3(cross(s3.v - v0, s2.v - v0)); continue; }
     break;
   }
+  if (portal_only) return true;
   bool hit = false;
   // #pragma unroll 1
   for (int it = 0;; it++) {
@@ -1105,7 +1123,8 @@ __device__ __forceinline__ CgShape cgShape(const DevModel& D, const SmemLayout& 
 #define CON_SWAP(x) (((x) >> 30) & 1)
 #define MAXHIT 4   // contacts of one candidate pair: plane - box gives up to four, plane - capsule two, everything else one
 // narrow phase for one candidate pair; returns the number of contacts (0..MAXHIT) with dist < margin
-__device__ __noinline__ int collidePair(int slot, SP sm, int pr, Hit* h, int* swapped) {
+// (filter: convex pairs only run the portal search; -1 = a portal exists, run the pair in full)
+__device__ __noinline__ int collidePair(int slot, SP sm, int pr, Hit* h, int* swapped, bool filter = false) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
   int c1 = D.pair_cg1[pr], c2 = D.pair_cg2[pr];
   const bool ovr = tP[slot].F.p[MYO_F_GEOM_TYPE_OVR] != nullptr;
@@ -1172,7 +1191,8 @@ __device__ __noinline__ int collidePair(int slot, SP sm, int pr, Hit* h, int* sw
     A.type = t1; A.pos = mkd(p1.x, p1.y, p1.z); A.mat = R1; A.size = mkd(sz1.x, sz1.y, sz1.z); A.margin = 0.5 * (double)margin;
     B.type = t2; B.pos = mkd(p2.x, p2.y, p2.z); B.mat = R2; B.size = mkd(sz2.x, sz2.y, sz2.z); B.margin = 0.5 * (double)margin;
     double depth; d3 nrm, pos;
-    if (!mprPenetration(A, B, 1e-6, 50, &depth, &nrm, &pos)) return 0;
+    if (!mprPenetration(A, B, 1e-6, 50, &depth, &nrm, &pos, filter)) return 0;
+    if (filter) return -1;
     h[0].dist = (float)((double)margin - depth); h[0].pos = mk3((float)pos.x, (float)pos.y, (float)pos.z);
     h[0].nrm = mk3((float)nrm.x, (float)nrm.y, (float)nrm.z);
   }
@@ -1199,14 +1219,15 @@ enum { E_D = 0, E_AREF, E_JAR, E_JV, E_FORCE, E_DESC0, E_COEF, E_DESC1, E_POS, E
 #define EFCI(k, r) __float_as_int(sm[L.efc + (k) * D.njmax + (r)])
 
 // ------------------------------------------------------------------------------------------ contact / efc outputs
-__device__ __noinline__ void writeConstraintOutputs(int slot, int fslot, SP sm, Tm t, World W, int ncon, int nefc, int niter) {
+// (efc_force and solver_niter, the results of the solve, are written by finishKernel: these records are complete once the
+// rows exist, and go out while the solver runs)
+__device__ __noinline__ void writeConstraintOutputs(int slot, int fslot, SP sm, Tm t, World W, int ncon, int nefc) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L; const FieldPtrs& F = tP[fslot].F;
   const int nv = D.nv, ncm = D.nconmax, njm = D.njmax;
   void* p;
   if (t.tl == 0) {
     if ((p = F.p[MYO_F_NCON])) OUTI(p, 0) = ncon;
     if ((p = F.p[MYO_F_NEFC])) OUTI(p, 0) = nefc;
-    if ((p = F.p[MYO_F_SOLVER_NITER])) OUTI(p, 0) = niter;
   }
   void* cg = F.p[MYO_F_CONTACT_GEOM]; void* cdim = F.p[MYO_F_CONTACT_DIM]; void* cadr = F.p[MYO_F_CONTACT_EFC_ADDRESS];
   void* cdist = F.p[MYO_F_CONTACT_DIST]; void* cpos = F.p[MYO_F_CONTACT_POS]; void* cfr = F.p[MYO_F_CONTACT_FRAME];
@@ -1239,15 +1260,14 @@ __device__ __noinline__ void writeConstraintOutputs(int slot, int fslot, SP sm, 
     }
   }
   void* epos = F.p[MYO_F_EFC_POS]; void* emar = F.p[MYO_F_EFC_MARGIN]; void* eD = F.p[MYO_F_EFC_D]; void* earef = F.p[MYO_F_EFC_AREF];
-  void* efrc = F.p[MYO_F_EFC_FORCE]; void* etyp = F.p[MYO_F_EFC_TYPE]; void* eJ = F.p[MYO_F_EFC_J];
-  if (epos || emar || eD || earef || efrc || etyp || eJ) {
+  void* etyp = F.p[MYO_F_EFC_TYPE]; void* eJ = F.p[MYO_F_EFC_J];
+  if (epos || emar || eD || earef || etyp || eJ) {
     TFOR(r, njm) {
       const bool on = r < nefc;
       if (epos) OUTF(epos, r) = on ? EFC(E_POS, r) : 0.f;
       if (emar) OUTF(emar, r) = on ? EFC(E_MARGIN, r) : 0.f;
       if (eD) OUTF(eD, r) = on ? EFC(E_D, r) : 0.f;
       if (earef) OUTF(earef, r) = on ? EFC(E_AREF, r) : 0.f;
-      if (efrc) OUTF(efrc, r) = on ? EFC(E_FORCE, r) : 0.f;
       const int d0 = on ? EFCI(E_DESC0, r) : 0, type = d0 & 3, id = d0 >> 2;
       if (etyp) OUTI(etyp, r) = !on ? -1 : (type == ROW_EQ ? 0 : (type == ROW_LIMJ ? 3 : (type == ROW_LIMT ? 4 : (EFCI(E_DESC1, r) < 0 ? 5 : 6))));
       if (eJ) {

@@ -134,6 +134,7 @@ struct TileAux {
   int* mpr_count;   // entries appended so far (zeroed before every collision pass)
   int mpr_cap;
   long long* dbg;   // developer timing of the solver phases ([tiles][32] clock64 sums; MYO_NEWTON_TIMING), else null
+  int tl_off;   // developer timeline (MYO_NEWTON_TIMING): dbg + tl_off = [kernel][start, end] in globaltimer ns
 };
 
 #endif  // MYO_DEVMODEL_H_

@@ -43,6 +43,17 @@ enum { FIN_EULER = 1, FIN_STATE = 2, FIN_WARM = 4, FIN_ACC = 8 };
 enum { WS_STATUS = 0, WS_TIME = 1, WS_SKIP = 2 };
 
 struct Ctx { SP sm; Tm t; World W; bool live; };
+// developer timeline (MYO_NEWTON_TIMING): first start and last end of each kernel's CTAs, globaltimer ns
+struct Timeline {
+  unsigned long long* p;
+  __device__ __forceinline__ static unsigned long long now() { unsigned long long v; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(v)); return v; }
+  __device__ __forceinline__ Timeline(int slot, int k) {
+    long long* d = tP[slot].X.dbg;
+    p = (d && threadIdx.x == 0) ? (unsigned long long*)d + tP[slot].X.tl_off + 2 * k : nullptr;
+    if (p) atomicMin(p, now());
+  }
+  __device__ __forceinline__ ~Timeline() { if (p) atomicMax(p + 1, now()); }
+};
 __device__ __forceinline__ Ctx tileCtx(int slot, int nworld, const int* mask, float* scratch) {
   Ctx c;
   const int lane = threadIdx.x & 31;
@@ -58,6 +69,8 @@ __device__ __forceinline__ Ctx tileCtx(int slot, int nworld, const int* mask, fl
 __global__ void __launch_bounds__(32 * MAXW, MINB_KIN) kinKernel(int slot, int fslot, int nworld, const int* __restrict__ mask, int flags,
                                                  float* __restrict__ scratch) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L; const FieldPtrs& F = tP[slot].F;
+  Timeline tline(slot, MYO_K_KIN);
+  if (blockIdx.x == 0 && threadIdx.x == 0 && tP[slot].X.mpr_count) *tP[slot].X.mpr_count = 0;   // the convex narrow phase's work list (collideKernel appends)
   Ctx c = tileCtx(slot, nworld, mask, scratch);
   if (!c.live) return;   // exited lanes are not waited for by the CTA barriers below
   SP sm = c.sm; Tm t = c.t; World W = c.W;
@@ -104,6 +117,7 @@ __global__ void __launch_bounds__(32 * MAXW, MINB_KIN) kinKernel(int slot, int f
 
 // ------------------------------------------------------------------------------------------ tendon: mj_tendon (+ path points)
 __global__ void __launch_bounds__(32 * MAXW, MINB_TENDON) tendonKernel(int slot, int fslot, int nworld, const int* __restrict__ mask, float* __restrict__ scratch) {
+  Timeline tline(slot, MYO_K_TENDON);
   Ctx c = tileCtx(slot, nworld, mask, scratch);
   if (!c.live) return;
   tendons(slot, fslot, c.sm, c.t, c.W);
@@ -113,6 +127,7 @@ __global__ void __launch_bounds__(32 * MAXW, MINB_TENDON) tendonKernel(int slot,
 __global__ void __launch_bounds__(32 * MAXW, MINB_INERTIA) inertiaKernel(int slot, int fslot, int nworld, const int* __restrict__ mask, int euler,
                                                      float* __restrict__ scratch) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
+  Timeline tline(slot, MYO_K_INERTIA);
   Ctx c = tileCtx(slot, nworld, mask, scratch);
   if (!c.live) return;
   SP sm = c.sm; Tm t = c.t;
@@ -124,16 +139,20 @@ __global__ void __launch_bounds__(32 * MAXW, MINB_INERTIA) inertiaKernel(int slo
     TSYNC();
     factorLDL(slot, sm + L.qH, sm + L.qHinv, t);
   }
+  TSYNC();
+  velocityBody(slot, fslot, sm, t, c.W);   // (cdof_dot was inertia()'s scratch up to here)
 }
 
 // ------------------------------------------------------------------------------------------ velact: mj_fwdVelocity, mj_fwdActuation, mj_fwdAcceleration
 __global__ void __launch_bounds__(32 * MAXW, MINB_VELACT) velactKernel(int slot, int fslot, int nworld, const int* __restrict__ mask, int posvel,
                                                     float* __restrict__ scratch) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
+  Timeline tline(slot, MYO_K_VELACT);
   Ctx c = tileCtx(slot, nworld, mask, scratch);
   if (!c.live) return;
   SP sm = c.sm; Tm t = c.t; World W = c.W;
-  velocity(slot, fslot, sm, t, W);
+  if (posvel) velocityBody(slot, fslot, sm, t, W);   // (a full pass has it from inertiaKernel)
+  velocityTendon(slot, fslot, sm, t, W);
   if (posvel) {   // mj_transmission outputs of the refreshed tendon stage (actuation() writes them on a full pass)
     const FieldPtrs& F = tP[fslot].F;
     void* olen = F.p[MYO_F_ACTUATOR_LENGTH]; void* ovel = F.p[MYO_F_ACTUATOR_VELOCITY];
@@ -183,6 +202,7 @@ __device__ __forceinline__ bool isMprPair(const DevModel& D, const SmemLayout& L
 // 32 floats = hit count, up to MAXHIT hits (dist, pos, normal).
 __global__ void __launch_bounds__(32 * MAXW, MINB_COLLIDE) collideKernel(int slot, int nworld, const int* __restrict__ mask, float* __restrict__ scratch) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L; const TileAux& X = tP[slot].X;
+  Timeline tline(slot, MYO_K_COLLIDE);
   Ctx c = tileCtx(slot, nworld, mask, scratch);
   if (!c.live) return;
   SP sm = c.sm; Tm t = c.t;
@@ -259,25 +279,47 @@ __global__ void __launch_bounds__(32 * MAXW, MINB_COLLIDE) collideKernel(int slo
 }
 // collide MPR: one listed (world, survivor) pair per lane, all lanes busy; the result goes to the survivor's own record, so
 // the (atomic) order of the list does not matter
+#define MPR_BATCH 512
 __global__ void __launch_bounds__(128) collideMprKernel(int slot, float* __restrict__ scratch) {
   const SmemLayout& L = tP[slot].L; const TileAux& X = tP[slot].X;
+  Timeline tline(slot, MYO_K_COLLIDE_MPR);
   const int n = min(*X.mpr_count, X.mpr_cap);
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+  // Two passes per batch of MPR_BATCH pairs: most pairs of the list are separated and leave the portal search after one or
+  // two support evaluations, a few run tens of refinement steps.  One pair per lane straight through leaves ~5 of 32 lanes
+  // busy (ncu: 5.25 threads per instruction); so the batch is filtered first, and the pairs that have a portal are
+  // compacted in shared memory and run in full by consecutive lanes.  (Each record has its own slot: order is free.)
+  __shared__ int sList[MPR_BATCH];
+  __shared__ int sCount;
+  auto record = [&](int i, bool filter) {
     const int2 e = X.mpr_list[i];
     SP sm; sm.p = scratch + (size_t)(e.x >> 5) * L.total * SCR + (e.x & 31);
     const int pr = __float_as_int(sm[L.cand + e.y]);
     Hit h[MAXHIT];
     int sw;
-    const int nh = collidePair(slot, sm, pr, h, &sw);
+    const int nh = collidePair(slot, sm, pr, h, &sw, filter);
+    if (nh < 0) return false;
     auto o = sm + L.ctmp + 32 * e.y;
     o[0] = __int_as_float(nh | (sw << 8));
     if (nh) { o[1] = h[0].dist; st3(o + 2, h[0].pos); st3(o + 5, h[0].nrm); }
+    return true;
+  };
+  const int batch = min(MPR_BATCH, max((int)blockDim.x, (int)(((n + gridDim.x - 1) / gridDim.x + blockDim.x - 1) / blockDim.x * blockDim.x)));
+  for (int base = blockIdx.x * batch; base < n; base += gridDim.x * batch) {
+    if (threadIdx.x == 0) sCount = 0;
+    __syncthreads();
+    for (int k = threadIdx.x; k < batch && base + k < n; k += blockDim.x)
+      if (!record(base + k, true)) sList[atomicAdd(&sCount, 1)] = base + k;
+    __syncthreads();
+    const int m = sCount;
+    for (int k = threadIdx.x; k < m; k += blockDim.x) record(sList[k], false);
+    __syncthreads();
   }
 }
 // collide B: in-order compaction of the hits into contact records -- contact order (hence geom1 / geom2 / efc_address) is
 // MuJoCo's
 __global__ void __launch_bounds__(32 * MAXW, 2) collideCompactKernel(int slot, int nworld, const int* __restrict__ mask, float* __restrict__ scratch) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
+  Timeline tline(slot, MYO_K_COLLIDE_COMPACT);
   Ctx c = tileCtx(slot, nworld, mask, scratch);
   const unsigned lmask = __ballot_sync(0xffffffffu, c.live);
   if (!c.live) return;
@@ -692,39 +734,129 @@ __device__ __noinline__ void hessianUpdate(int slot, SP sm, Tm t, SP H, int nefc
   TSYNC();
   TFOR(i, TRI(nv)) sm[L.Hsave + i] = H[i];
 }
-// left-looking Cholesky of H in place, warps over rows; the diagonal of the factor goes to Hd (H keeps the unscaled pivot)
+// Blocked left-looking Cholesky of H in place (L L^T = H), panels of CHB columns, two barriers per panel: (1) every row at
+// or below the panel takes the finished columns out of its panel entries (rows over warps); (2) every warp factors the
+// CHB x CHB diagonal block in registers -- redundantly, which saves the barrier a single owner would need -- and solves
+// its rows below against it.  The factor's diagonal goes to Hd (the solve divides by it).  All branches are warp-uniform.
+#define CHB 6
+#define CHT(a, b) ((a) * ((a) + 1) / 2 + (b))
 __device__ __noinline__ void choleskyTile(int nv, SP H, SP Hd, Tm t) {
   const int nw = t.nw;
   TSYNC();
-  for (int j = 0; j < nv; j++) {
-    for (int r = j + t.tl; r < nv; r += nw) {
-      auto Hr = H + TRI(r); auto Hj = H + TRI(j);
-      float s0 = Hr[j], s1 = 0.f;
-      int k = 0;
-      HOT
-      for (; k + 1 < j; k += 2) { s0 = fmaf(-Hr[k], Hj[k], s0); s1 = fmaf(-Hr[k + 1], Hj[k + 1], s1); }
-      if (k < j) s0 = fmaf(-Hr[k], Hj[k], s0);
-      Hr[j] = s0 + s1;
+  for (int j0 = 0; j0 < nv; j0 += CHB) {
+    const int pb = min(CHB, nv - j0);
+    if (j0 > 0) {
+      for (int r = j0 + t.tl; r < nv; r += nw) {
+        auto Hr = H + TRI(r);
+        const int cn = min(r - j0 + 1, pb);
+        float acc[CHB];
+#pragma unroll
+        for (int c = 0; c < CHB; c++) acc[c] = c < cn ? Hr[j0 + c] : 0.f;
+        SP Hc[CHB];
+#pragma unroll
+        for (int c = 0; c < CHB; c++) Hc[c] = H + TRI(min(j0 + c, nv - 1));   // (past the panel: computed, not stored)
+#pragma unroll 2
+        for (int k = 0; k < j0; k++) {
+          const float a = Hr[k];
+#pragma unroll
+          for (int c = 0; c < CHB; c++) acc[c] = fmaf(-a, Hc[c][k], acc[c]);
+        }
+#pragma unroll
+        for (int c = 0; c < CHB; c++) if (c < cn) Hr[j0 + c] = acc[c];
+      }
+      TSYNC();
     }
-    TSYNC();
-    const float d = sqrtf(fmaxf(H[TRI(j) + j], MINVAL)), inv = 1.f / d;
-    for (int r = j + 1 + t.tl; r < nv; r += nw) H[TRI(r) + j] *= inv;
-    if (t.tl == 0) Hd[j] = d;
+    float l[CHB * (CHB + 1) / 2], inv[CHB];
+#pragma unroll
+    for (int a = 0; a < CHB; a++)
+#pragma unroll
+      for (int b = 0; b <= a; b++) l[CHT(a, b)] = a < pb ? H[TRI(j0 + a) + j0 + b] : (a == b ? 1.f : 0.f);
+#pragma unroll
+    for (int a = 0; a < CHB; a++)
+#pragma unroll
+      for (int b = 0; b <= a; b++) {
+        float sacc = l[CHT(a, b)];
+#pragma unroll
+        for (int k = 0; k < b; k++) sacc = fmaf(-l[CHT(a, k)], l[CHT(b, k)], sacc);
+        if (b < a) l[CHT(a, b)] = sacc * inv[b];
+        else { const float d = sqrtf(fmaxf(sacc, MINVAL)); l[CHT(a, a)] = d; inv[a] = 1.f / d; }
+      }
+    if (t.tl == 0) {
+#pragma unroll
+      for (int a = 0; a < CHB; a++) if (a < pb) {
+#pragma unroll
+        for (int b = 0; b < a; b++) H[TRI(j0 + a) + j0 + b] = l[CHT(a, b)];
+        Hd[j0 + a] = l[CHT(a, a)];
+      }
+    }
+    for (int r = j0 + pb + t.tl; r < nv; r += nw) {
+      auto Hr = H + TRI(r);
+      float x[CHB];
+#pragma unroll
+      for (int b = 0; b < CHB; b++) {
+        float sacc = b < pb ? Hr[j0 + b] : 0.f;
+#pragma unroll
+        for (int k = 0; k < b; k++) sacc = fmaf(-x[k], l[CHT(b, k)], sacc);
+        x[b] = sacc * inv[b];
+      }
+#pragma unroll
+      for (int b = 0; b < CHB; b++) if (b < pb) Hr[j0 + b] = x[b];
+    }
     TSYNC();
   }
 }
-// x <- (L L^T)^-1 x with the factor above; y is a scratch vector (one barrier per column each way)
+// x <- (L L^T)^-1 x with the factor above; y is a scratch vector.  Same panels, one barrier per panel each way: every warp
+// solves the panel's own unknowns redundantly, then takes them out of the rows it owns.
 __device__ __noinline__ void cholSolveTile(int nv, SP H, SP Hd, SP x, SP y, Tm t) {
-  for (int j = 0; j < nv; j++) {
-    const float xj = x[j] / Hd[j];
-    if (t.tl == 0) y[j] = xj;
-    for (int r = j + 1 + t.tl; r < nv; r += t.nw) x[r] = fmaf(-H[TRI(r) + j], xj, x[r]);
+  const int nw = t.nw;
+  for (int j0 = 0; j0 < nv; j0 += CHB) {
+    const int pb = min(CHB, nv - j0);
+    float yb[CHB];
+#pragma unroll
+    for (int b = 0; b < CHB; b++) {
+      const int jb = min(j0 + b, nv - 1);
+      float sacc = x[jb];
+#pragma unroll
+      for (int k = 0; k < b; k++) sacc = fmaf(-H[TRI(jb) + j0 + k], yb[k], sacc);
+      yb[b] = b < pb ? sacc / Hd[jb] : 0.f;
+    }
+    if (t.tl == 0) {
+#pragma unroll
+      for (int b = 0; b < CHB; b++) if (b < pb) y[j0 + b] = yb[b];
+    }
+    for (int r = j0 + pb + t.tl; r < nv; r += nw) {
+      auto Hr = H + TRI(r) + j0;
+      float sacc = x[r];
+#pragma unroll
+      for (int b = 0; b < CHB; b++) if (b < pb) sacc = fmaf(-Hr[b], yb[b], sacc);
+      x[r] = sacc;
+    }
     TSYNC();
   }
-  for (int j = nv - 1; j >= 0; j--) {
-    const float xj = y[j] / Hd[j];
-    if (t.tl == 0) x[j] = xj;
-    for (int r = t.tl; r < j; r += t.nw) y[r] = fmaf(-H[TRI(j) + r], xj, y[r]);
+  for (int j0 = ((nv - 1) / CHB) * CHB; j0 >= 0; j0 -= CHB) {
+    const int pb = min(CHB, nv - j0);
+    float zb[CHB];
+#pragma unroll
+    for (int bb = 0; bb < CHB; bb++) {
+      const int b = CHB - 1 - bb;
+      zb[b] = 0.f;
+      if (b < pb) {
+        float sacc = y[j0 + b];
+#pragma unroll
+        for (int k = b + 1; k < CHB; k++) if (k < pb) sacc = fmaf(-H[TRI(j0 + k) + j0 + b], zb[k], sacc);
+        zb[b] = sacc / Hd[j0 + b];
+      }
+    }
+    if (t.tl == 0) {
+#pragma unroll
+      for (int b = 0; b < CHB; b++) if (b < pb) x[j0 + b] = zb[b];
+    }
+    for (int r = t.tl; r < j0; r += nw) {
+      float sacc = y[r];
+#pragma unroll
+      for (int b = 0; b < CHB; b++) if (b < pb) sacc = fmaf(-H[TRI(j0 + b) + r], zb[b], sacc);
+      y[r] = sacc;
+    }
     TSYNC();
   }
 }
@@ -917,6 +1049,21 @@ __device__ __noinline__ int newtonTile(int slot, SP sm, Tm t, const NewtonMem& M
 
 // Shared memory of a tile: Hessian (lower triangle), its factor's diagonal and six nv-vectors, [element][32 lanes].  When a
 // model's block does not fit (nv beyond ~55), the same kernel runs with everything in the world's scratch column.
+// mj_makeConstraint as its own launch: it needs the contacts and the velocity, not the smooth forces, so it runs on the
+// collision stream beside the tendon / actuation stages (models with tendon limits: after them, api.cu).
+__global__ void __launch_bounds__(32 * MAXW, MINB_NEWTON) makeconKernel(int slot, int nworld, const int* __restrict__ mask, float* __restrict__ scratch) {
+  const SmemLayout& L = tP[slot].L;
+  Timeline tline(slot, MYO_K_MAKECON);
+  Ctx c = tileCtx(slot, nworld, mask, scratch);
+  const unsigned lmask = __ballot_sync(0xffffffffu, c.live);
+  if (!c.live) return;
+  SP sm = c.sm; Tm t = c.t;
+  int status = __float_as_int(sm[L.wstate + WS_STATUS]);
+  const int ncon = __float_as_int(sm[L.counts]);
+  const int nconT = __reduce_max_sync(lmask, ncon);
+  const int nefc = makeConstraintTile(slot, sm, t, ncon, nconT, &status);
+  if (t.tl == 0) { sm[L.counts + 1] = __int_as_float(nefc); sm[L.wstate + WS_STATUS] = __int_as_float(status); }
+}
 static inline size_t newtonSmemFloats(int nv) { return (size_t)(TRI(nv) + 7 * nv) * 32; }
 #define NEWTON_SMEM_MAX (190 * 1024)   // + ~31 KB of static reduction / scan buffers <= 227 KB per CTA
 __global__ void __launch_bounds__(32 * MAXW, MINB_NEWTON) newtonKernel(int slot, int fslot, int nworld, const int* __restrict__ mask, int check_acc,
@@ -925,6 +1072,7 @@ __global__ void __launch_bounds__(32 * MAXW, MINB_NEWTON) newtonKernel(int slot,
   extern __shared__ float tileShared[];
   __shared__ int sBad[32];
   const int lane = threadIdx.x & 31;
+  Timeline tline(slot, MYO_K_NEWTON);
   Ctx c = tileCtx(slot, nworld, mask, scratch);
   const unsigned lmask = __ballot_sync(0xffffffffu, c.live);
   if (!c.live) return;
@@ -935,8 +1083,7 @@ __global__ void __launch_bounds__(32 * MAXW, MINB_NEWTON) newtonKernel(int slot,
   const int nconT = __reduce_max_sync(lmask, ncon);
   if (t.tl == 0) sBad[lane] = 0;
   long long* dbg = tP[slot].X.dbg; long long tlast = dbg ? clock64() : 0;
-  int nefc = makeConstraintTile(slot, sm, t, ncon, nconT, &status);
-  TICK(0);
+  const int nefc = __float_as_int(sm[L.counts + 1]);   // rows: makeconKernel
   const int nefcT = __reduce_max_sync(lmask, nefc);
   int niter = 0;
   if (nefcT == 0) {   // tile-uniform
@@ -973,7 +1120,7 @@ __global__ void __launch_bounds__(32 * MAXW, MINB_NEWTON) newtonKernel(int slot,
   }
   if (fslot != MYO_NSLOT && D.nsensor > 0) touchSensors(slot, fslot, sm, t, c.W, nefc > 0 ? ncon : 0);
   if (t.tl == 0) {
-    sm[L.counts + 1] = __int_as_float(nefc); sm[L.counts + 2] = __int_as_float(niter);
+    sm[L.counts + 2] = __int_as_float(niter);
     sm[L.wstate + WS_STATUS] = __int_as_float(status); sm[L.wstate + WS_SKIP] = __int_as_float(skip);
   }
 }
@@ -984,6 +1131,7 @@ __global__ void __launch_bounds__(32 * MAXW, MINB_NEWTON) newtonKernel(int slot,
 __global__ void __launch_bounds__(32 * MAXW, MINB_FINISH) finishKernel(int slot, int fslot, int nworld, const int* __restrict__ mask, int flags,
                                                     float* __restrict__ scratch) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L; const FieldPtrs& F = tP[slot].F;
+  Timeline tline(slot, MYO_K_FINISH);
   Ctx c = tileCtx(slot, nworld, mask, scratch);
   if (!c.live) return;
   SP sm = c.sm; Tm t = c.t; World W = c.W;
@@ -994,6 +1142,8 @@ __global__ void __launch_bounds__(32 * MAXW, MINB_FINISH) finishKernel(int slot,
     if ((o = Fo.p[MYO_F_QACC])) TFOR(i, nv) OUTF(o, i) = sm[L.qacc + i];
     if ((o = Fo.p[MYO_F_QFRC_CONSTRAINT])) TFOR(i, nv) OUTF(o, i) = sm[L.qfrc_con + i];
     if ((o = Fo.p[MYO_F_QFRC_INVERSE])) TFOR(i, nv) OUTF(o, i) = 0.f;
+    if ((o = Fo.p[MYO_F_EFC_FORCE])) { const int nefc = __float_as_int(sm[L.counts + 1]); TFOR(r, D.njmax) OUTF(o, r) = r < nefc ? EFC(E_FORCE, r) : 0.f; }
+    if ((o = Fo.p[MYO_F_SOLVER_NITER]) && t.tl == 0) OUTI(o, 0) = __float_as_int(sm[L.counts + 2]);
   }
   if (flags & FIN_EULER) {
     const bool skip = __float_as_int(sm[L.wstate + WS_SKIP]) != 0;   // mj_checkAcc reset this world: nothing to integrate
@@ -1055,11 +1205,12 @@ __global__ void __launch_bounds__(32 * MAXW, MINB_FINISH) finishKernel(int slot,
 // the items are striped over the warps of gridDim.y CTAs per tile.
 __global__ void __launch_bounds__(256) conoutKernel(int slot, int fslot, int nworld, const int* __restrict__ mask, float* __restrict__ scratch) {
   const SmemLayout& L = tP[slot].L;
+  Timeline tline(slot, MYO_K_CONOUT);
   Ctx c = tileCtx(slot, nworld, mask, scratch);
   if (!c.live) return;
   Tm t; t.nw = c.t.nw * gridDim.y; t.tl = blockIdx.y * c.t.nw + c.t.tl;
   SP sm = c.sm;
-  writeConstraintOutputs(slot, fslot, sm, t, c.W, __float_as_int(sm[L.counts]), __float_as_int(sm[L.counts + 1]), __float_as_int(sm[L.counts + 2]));
+  writeConstraintOutputs(slot, fslot, sm, t, c.W, __float_as_int(sm[L.counts]), __float_as_int(sm[L.counts + 1]));
 }
 
 // known-answer hook for the rotation helpers above (tests/: reference KATs of myosuite/utils/quat_math.py)
@@ -1085,6 +1236,10 @@ int myo_tile_upload(int slot, const DevModel& D, const SmemLayout& L, const Fiel
   P.D = D; P.L = L; P.F = F; P.X = X;
   return cudaMemcpyToSymbolAsync(tP, &P, sizeof(TParams), (size_t)slot * sizeof(TParams), cudaMemcpyHostToDevice, (cudaStream_t)stream) == cudaSuccess ? 0 : -1;
 }
+// An empty launch: api.cu puts one in front of the tendon and inertia kernels so that the collision kernel, which becomes
+// ready at the same instant (end of kin) and heads the longest branch, gets its CTAs onto the SMs first.
+__global__ void nopKernel() {}
+int myo_nop_launch(void* stream) { nopKernel<<<1, 32, 0, (cudaStream_t)stream>>>(); return cudaGetLastError() == cudaSuccess ? 0 : -1; }
 static int envInt(const char* name, int dflt) { const char* e = getenv(name); return e ? atoi(e) : dflt; }
 // Warps per tile of each kernel (developer knobs MYO_NW_*): enough warps per SM to hide the scratch latency, few enough
 // that the item loops still have work for every warp.
@@ -1095,7 +1250,7 @@ int myo_tile_launch(int kernel, int slot, int fslot, int nworld, const int* mask
   // solver (8: +6.6 % step time, 10: +3.9 %, 16 at <= 64 registers: +1.8 %); the tendon phase prefers 8.
   static const int nwKin = envInt("MYO_NW_KIN", 12), nwTen = envInt("MYO_NW_TEN", 8), nwIne = envInt("MYO_NW_INE", 8),
                    nwCol = envInt("MYO_NW_COL", 12), nwVel = envInt("MYO_NW_VEL", 12), nwFin = envInt("MYO_NW_FIN", 8),
-                   nwOut = envInt("MYO_NW_OUT", 8), yOut = envInt("MYO_Y_OUT", 4), nwNew = envInt("MYO_NW_NEWTON", 12);
+                   nwOut = envInt("MYO_NW_OUT", 8), yOut = envInt("MYO_Y_OUT", 4), nwNew = envInt("MYO_NW_NEWTON", 12), nwMak = envInt("MYO_NW_MAKECON", 12);
   const int tiles = (nworld + 31) / 32;
   cudaStream_t st = (cudaStream_t)stream;
   switch (kernel) {
@@ -1123,6 +1278,7 @@ int myo_tile_launch(int kernel, int slot, int fslot, int nworld, const int* mask
       }
       newtonKernel<<<tiles, 32 * nwNew, shmem, st>>>(slot, fslot, nworld, mask, flags & 1, use_smem, scratch);
     } break;
+    case MYO_K_MAKECON: makeconKernel<<<tiles, 32 * nwMak, 0, st>>>(slot, nworld, mask, scratch); break;
     case MYO_K_CONOUT: conoutKernel<<<dim3(tiles, yOut), 32 * nwOut, 0, st>>>(slot, fslot, nworld, mask, scratch); break;
     default: return -1;
   }

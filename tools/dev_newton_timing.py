@@ -15,13 +15,15 @@ def run(n0, n1):
     for i in range(n0, n1):
         if i % 10 == 0: d.storage("ctrl").copy_(partition.ctrl_hash_torch(m.nu, 0, nw, 1234, i // 10, "cuda"))
         mjx.step(model, d, 1)
-run(0, 300)
+A, B = (int(sys.argv[1]), int(sys.argv[2])) if len(sys.argv) > 2 else (300, 400)
+run(0, A)
 n = L.myo_debug_timing(d._h, None)
 a = np.zeros(n, dtype=np.int64); L.myo_debug_timing(d._h, a.ctypes.data_as(ctypes.c_void_p)); a0 = a.reshape(-1, 32).copy()
-run(300, 400)
+run(A, B)
 L.myo_debug_timing(d._h, a.ctypes.data_as(ctypes.c_void_p)); a1 = a.reshape(-1, 32) - a0
 names = ["makeConstraint", "warm start / residuals", "force + gradient", "hessian assemble", "hessian update", "cholesky", "chol solve", "M s, J s", "line search", "update + cost", "final force", "passes"]
-per = a1 / 100.0
+per = a1 / float(B - A)
+print("steps", A, B, "ncon mean %.2f nefc mean %.2f max %d" % (float(d.ncon.float().mean()), float(d.nefc.float().mean()), int(d.nefc.max())))
 tot = per[:, :11].sum(axis=1)
 print("tiles", len(per), "cycles per tile per step: mean %.0f  p50 %.0f  max %.0f  (%.1f us at 1.965 GHz max)" % (tot.mean(), np.median(tot), tot.max(), tot.max() / 1965))
 print("passes per tile per step: mean %.2f max %.2f" % (per[:, 11].mean(), per[:, 11].max()))
