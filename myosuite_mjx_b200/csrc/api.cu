@@ -410,7 +410,7 @@ int myo_debug_timeline(myo_batch* b, unsigned long long* host_out) {
   if (cudaDeviceSynchronize() != cudaSuccess) return -1;
   if (host_out && cudaMemcpy(host_out, p, 64 * sizeof(long long), cudaMemcpyDeviceToHost) != cudaSuccess) return -1;
   unsigned long long arm[64];
-  for (int i = 0; i < 64; i++) arm[i] = (i & 1) ? 0ull : ~0ull;
+  for (int i = 0; i < 64; i++) arm[i] = ((i & 1) || i >= 48) ? 0ull : ~0ull;
   return cudaMemcpy(p, arm, sizeof(arm), cudaMemcpyHostToDevice) == cudaSuccess ? 64 : -1;
 }
 int myo_kat_quat(int n, const float* qa, const float* qb, float* prod, float* mat, float* rotated, void* stream) {

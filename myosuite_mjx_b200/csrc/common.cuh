@@ -1017,10 +1017,16 @@ __device__ __forceinline__ d3 operator*(d3 a, double s) { return mkd(a.x * s, a.
 __device__ __forceinline__ double dot(d3 a, d3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
 __device__ __forceinline__ d3 cross(d3 a, d3 b) { return mkd(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x); }
 __device__ __forceinline__ double norm3(d3 a) { return sqrt(dot(a, a)); }
-__device__ __forceinline__ d3 unit3(d3 a) { const double n = norm3(a); return n < 1e-15 ? mkd(1.0, 0.0, 0.0) : a * (1.0 / n); }
-struct Shape { int type; d3 pos; SP mat; d3 size; double margin; };
-__device__ __noinline__ d3 supportPt(const Shape& s, d3 dir) {
-  auto R = s.mat;
+__device__ __forceinline__ d3 unit3(d3 a) { const double q = dot(a, a); return q < 1e-30 ? mkd(1.0, 0.0, 0.0) : a * rsqrt(q); }   // (one rsqrt instead of sqrt + divide: these sit on the portal iteration's dependent chain)
+// (the rotation is copied into the record once: the support function runs tens of times per pair; it and mprSup are
+// inlined so that the portal's support points stay in registers instead of going through the stack)
+struct Shape { int type; d3 pos; float mat[9]; d3 size; double margin; };
+__device__ __forceinline__ void shapeMat(Shape& s, SP R) {
+#pragma unroll
+  for (int i = 0; i < 9; i++) s.mat[i] = R[i];
+}
+__device__ __forceinline__ d3 supportPt(const Shape& s, d3 dir) {
+  const float* R = s.mat;
   const d3 d = mkd(R[0] * dir.x + R[3] * dir.y + R[6] * dir.z, R[1] * dir.x + R[4] * dir.y + R[7] * dir.z, R[2] * dir.x + R[5] * dir.y + R[8] * dir.z);
   d3 r = mkd(0.0, 0.0, 0.0);
   switch (s.type) {
@@ -1028,11 +1034,11 @@ __device__ __noinline__ d3 supportPt(const Shape& s, d3 dir) {
     case G_CAPSULE: r = d * s.size.x; r.z += d.z >= 0.0 ? s.size.y : -s.size.y; break;
     case G_ELLIPSOID: {
       const d3 t = mkd(s.size.x * s.size.x * d.x, s.size.y * s.size.y * d.y, s.size.z * s.size.z * d.z);
-      r = t * (1.0 / sqrt(fmax(1e-30, t.x * d.x + t.y * d.y + t.z * d.z)));
+      r = t * rsqrt(fmax(1e-30, t.x * d.x + t.y * d.y + t.z * d.z));
     } break;
     case G_CYLINDER: {
-      const double n = sqrt(d.x * d.x + d.y * d.y);
-      if (n > 1e-12) { r.x = s.size.x * d.x / n; r.y = s.size.x * d.y / n; }
+      const double q = d.x * d.x + d.y * d.y;
+      if (q > 1e-24) { const double in = s.size.x * rsqrt(q); r.x = d.x * in; r.y = d.y * in; }
       r.z = d.z >= 0.0 ? s.size.y : -s.size.y;
     } break;
     case G_BOX: r = mkd(d.x >= 0.0 ? s.size.x : -s.size.x, d.y >= 0.0 ? s.size.y : -s.size.y, d.z >= 0.0 ? s.size.z : -s.size.z); break;
@@ -1041,12 +1047,12 @@ __device__ __noinline__ d3 supportPt(const Shape& s, d3 dir) {
   return mkd(R[0] * r.x + R[1] * r.y + R[2] * r.z, R[3] * r.x + R[4] * r.y + R[5] * r.z, R[6] * r.x + R[7] * r.y + R[8] * r.z) + s.pos + dir * s.margin;
 }
 struct Sup { d3 v, a, b; };
-__device__ __noinline__ Sup mprSup(const Shape& A, const Shape& B, d3 d) {
+__device__ __forceinline__ Sup mprSup(const Shape& A, const Shape& B, d3 d) {
   Sup s; s.a = supportPt(A, d * -1.0); s.b = supportPt(B, d); s.v = s.b - s.a; return s;
 }
 // portal_only: stop once a portal exists (true) -- every early "no intersection" exit lies before that point or in the first
 // refinement steps, so this is the cheap filter collideMprKernel compacts its work list with
-__device__ __noinline__ bool mprPenetration(const Shape& A, const Shape& B, double tol, int maxit, double* depth, d3* nrm, d3* pos, bool portal_only) {
+__device__ __forceinline__ bool mprPenetration(const Shape& A, const Shape& B, double tol, int maxit, double* depth, d3* nrm, d3* pos, bool portal_only) {
   d3 v0 = B.pos - A.pos;
   if (norm3(v0) < 1e-12) v0 = mkd(1e-5, 0.0, 0.0);
   d3 dir = unit3(v0 * -1.0);
@@ -1124,7 +1130,9 @@ __device__ __forceinline__ CgShape cgShape(const DevModel& D, const SmemLayout& 
 #define MAXHIT 4   // contacts of one candidate pair: plane - box gives up to four, plane - capsule two, everything else one
 // narrow phase for one candidate pair; returns the number of contacts (0..MAXHIT) with dist < margin
 // (filter: convex pairs only run the portal search; -1 = a portal exists, run the pair in full)
-__device__ __noinline__ int collidePair(int slot, SP sm, int pr, Hit* h, int* swapped, bool filter = false) {
+// (CONVEX = false: the tile kernel's instance, which never sees a convex pair -- isMprPair sends those to the work list --
+// and should not carry the MPR code's registers)
+template <bool CONVEX> __device__ __noinline__ int collidePair(int slot, SP sm, int pr, Hit* h, int* swapped, bool filter = false) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
   int c1 = D.pair_cg1[pr], c2 = D.pair_cg2[pr];
   const bool ovr = tP[slot].F.p[MYO_F_GEOM_TYPE_OVR] != nullptr;
@@ -1161,7 +1169,7 @@ __device__ __noinline__ int collidePair(int slot, SP sm, int pr, Hit* h, int* sw
         h[n].dist = cd; h[n].pos = p2 + corner - ax1 * (0.5f * cd); h[n].nrm = ax1; n++;
       }
     } else {
-      Shape s; s.type = t2; s.pos = mkd(p2.x, p2.y, p2.z); s.mat = R2; s.size = mkd(sz2.x, sz2.y, sz2.z); s.margin = 0.0;
+      Shape s; s.type = t2; s.pos = mkd(p2.x, p2.y, p2.z); shapeMat(s, R2); s.size = mkd(sz2.x, sz2.y, sz2.z); s.margin = 0.0;
       const d3 spd = supportPt(s, mkd(-ax1.x, -ax1.y, -ax1.z));
       const f3 sp = mk3((float)spd.x, (float)spd.y, (float)spd.z);
       const float dist = (float)((spd.x - p1.x) * ax1.x + (spd.y - p1.y) * ax1.y + (spd.z - p1.z) * ax1.z);
@@ -1186,10 +1194,11 @@ __device__ __noinline__ int collidePair(int slot, SP sm, int pr, Hit* h, int* sw
       x2 = clipf((v - mb * x1) / fmaxf(1e-30f, mc), -1.f, 1.f);
     }
     h[0] = sphereSphere(p1 + a1 * x1, sz1.x, p2 + a2 * x2, sz2.x);
-  } else {
+  } else if (!CONVEX) return 0;
+  else {
     Shape A, B;
-    A.type = t1; A.pos = mkd(p1.x, p1.y, p1.z); A.mat = R1; A.size = mkd(sz1.x, sz1.y, sz1.z); A.margin = 0.5 * (double)margin;
-    B.type = t2; B.pos = mkd(p2.x, p2.y, p2.z); B.mat = R2; B.size = mkd(sz2.x, sz2.y, sz2.z); B.margin = 0.5 * (double)margin;
+    A.type = t1; A.pos = mkd(p1.x, p1.y, p1.z); shapeMat(A, R1); A.size = mkd(sz1.x, sz1.y, sz1.z); A.margin = 0.5 * (double)margin;
+    B.type = t2; B.pos = mkd(p2.x, p2.y, p2.z); shapeMat(B, R2); B.size = mkd(sz2.x, sz2.y, sz2.z); B.margin = 0.5 * (double)margin;
     double depth; d3 nrm, pos;
     if (!mprPenetration(A, B, 1e-6, 50, &depth, &nrm, &pos, filter)) return 0;
     if (filter) return -1;

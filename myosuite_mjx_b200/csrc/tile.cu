@@ -258,7 +258,7 @@ __global__ void __launch_bounds__(32 * MAXW, MINB_COLLIDE) collideKernel(int slo
     if (!mp) {
       Hit h[MAXHIT];
       int sw;
-      const int n = collidePair(slot, sm, pr, h, &sw);
+      const int n = collidePair<false>(slot, sm, pr, h, &sw);
       auto o = tmp + 32 * k;
       o[0] = __int_as_float(n | (sw << 8));
       for (int q = 0; q < n; q++) { o[1 + 7 * q] = h[q].dist; st3(o + 2 + 7 * q, h[q].pos); st3(o + 5 + 7 * q, h[q].nrm); }
@@ -296,7 +296,7 @@ __global__ void __launch_bounds__(128) collideMprKernel(int slot, float* __restr
     const int pr = __float_as_int(sm[L.cand + e.y]);
     Hit h[MAXHIT];
     int sw;
-    const int nh = collidePair(slot, sm, pr, h, &sw, filter);
+    const int nh = collidePair<true>(slot, sm, pr, h, &sw, filter);
     if (nh < 0) return false;
     auto o = sm + L.ctmp + 32 * e.y;
     o[0] = __int_as_float(nh | (sw << 8));
@@ -311,6 +311,10 @@ __global__ void __launch_bounds__(128) collideMprKernel(int slot, float* __restr
       if (!record(base + k, true)) sList[atomicAdd(&sCount, 1)] = base + k;
     __syncthreads();
     const int m = sCount;
+    if (X.dbg && threadIdx.x == 0) {   // developer counters: pairs listed, pairs with a portal
+      unsigned long long* q = (unsigned long long*)X.dbg + X.tl_off + 48;
+      atomicAdd(q, (unsigned long long)min(batch, n - base)); atomicAdd(q + 1, (unsigned long long)m);
+    }
     for (int k = threadIdx.x; k < m; k += blockDim.x) record(sList[k], false);
     __syncthreads();
   }

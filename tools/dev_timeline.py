@@ -27,8 +27,10 @@ for s in range(N):
     a = np.array(buf[:2 * len(names)], dtype=np.float64).reshape(-1, 2)
     t0 = a[0, 0]
     acc += (a - t0) / 1e3; tot += (a[:, 1].max() - t0) / 1e3
+    mpr = np.array(buf[48:50], dtype=np.float64) if s == 0 else mpr
 acc /= N
 print("step %d..%d: kernel start / end / duration on the device clock, us from the start of kin (mean of %d steps, each synchronised)" % (A, A + N, N))
 for k in np.argsort(acc[:, 0]):
     print("%-16s %8.1f %8.1f %8.1f" % (names[k], acc[k, 0], acc[k, 1], acc[k, 1] - acc[k, 0]))
 print("step span %.1f us" % (tot / N))
+print("convex narrow phase, one step: pairs listed %d, with a portal %d (per world-step %.2f / %.2f)" % (mpr[0], mpr[1], mpr[0] / nw, mpr[1] / nw))
