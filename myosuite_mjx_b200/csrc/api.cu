@@ -287,6 +287,7 @@ static int launchPhases(myo_batch* b, int nsub, int forward_only, const int32_t*
     ok &= tile(MYO_K_KIN, fslot, (first ? (do_reset ? MYO_KIN_RESET : MYO_KIN_LOAD) : 0) | (forward_only ? 0 : MYO_KIN_CHECK)) == 0; STOP_HERE();
     // mj_makeConstraint needs the contacts and qvel only -- unless the model has tendon limits (tendon length / velocity)
     const bool makecon_early = b->D.nlimt == 0;
+    const bool posout = fslot != MYO_PARAM_SLOTS;   // (field tests are per pointer inside the kernel)
     const bool conout = last && b->conout;
     if (concurrent && !posvel && debug_stop < 0) {
       // fork after kin: collision chain (+ constraint rows, + records out) | tendon -> velact | inertia; join before the solver
@@ -294,20 +295,24 @@ static int launchPhases(myo_batch* b, int nsub, int forward_only, const int32_t*
       auto E = [&](int i) { return (cudaEvent_t)b->ev[i]; };
       const cudaStream_t main = (cudaStream_t)stream;
       ok &= cudaEventRecord(E(0), main) == cudaSuccess;
-      for (int i = 0; i < 3; i++) ok &= cudaStreamWaitEvent(S(i), E(0), 0) == cudaSuccess;
+      for (int i = 0; i < 4; i++) ok &= cudaStreamWaitEvent(S(i), E(0), 0) == cudaSuccess;
+      // output stream (lowest priority): the position stage's fields now, the contact / constraint records once the rows exist
+      static const int ndelay = getenv("MYO_DELAY") ? atoi(getenv("MYO_DELAY")) : 1;   // developer knob
+      if (posout) {
+        for (int i = 0; i < 2 * ndelay; i++) { g_launches++; ok &= myo_nop_launch(b->side[3]) == 0; }   // (behind tendon / inertia, see below)
+        cur = b->side[3]; ok &= tile(MYO_K_POSOUT, fslot, 0) == 0;
+      }
       static const bool conout_late = getenv("MYO_CONOUT_LATE") && atoi(getenv("MYO_CONOUT_LATE"));   // developer knob
       auto rows = [&](cudaStream_t on) {   // on the stream `cur` = `on`
         ok &= tile(MYO_K_MAKECON, fslot, 0) == 0;
         if (conout && !conout_late) {
           ok &= cudaEventRecord(E(3), on) == cudaSuccess && cudaStreamWaitEvent(S(3), E(3), 0) == cudaSuccess;
           void* keep = cur; cur = b->side[3]; ok &= tile(MYO_K_CONOUT, fslot, 0) == 0; cur = keep;
-          ok &= cudaEventRecord(E(4), S(3)) == cudaSuccess;
         }
       };
       cur = b->side[0]; ok &= collide(fslot);
       if (makecon_early) rows(S(0));
       ok &= cudaEventRecord(E(1), S(0)) == cudaSuccess;
-      static const int ndelay = getenv("MYO_DELAY") ? atoi(getenv("MYO_DELAY")) : 1;   // developer knob
       for (int i = 0; i < ndelay; i++) { g_launches += 2; ok &= myo_nop_launch(b->side[1]) == 0 && myo_nop_launch(b->side[2]) == 0; }
       cur = b->side[1]; ok &= tile(MYO_K_TENDON, fslot, 0) == 0;
       cur = b->side[2]; ok &= tile(MYO_K_INERTIA, fslot, forward_only ? 0 : 1) == 0;
@@ -317,17 +322,18 @@ static int launchPhases(myo_batch* b, int nsub, int forward_only, const int32_t*
       cur = stream;
       ok &= cudaStreamWaitEvent(main, E(1), 0) == cudaSuccess && cudaStreamWaitEvent(main, E(5), 0) == cudaSuccess;
       if (!makecon_early) rows(main);
-      ok &= tile(MYO_K_NEWTON, fslot, (forward_only ? 0 : 1) | (b->D.nv << 8)) == 0;
+      const int fin = (forward_only ? 0 : MYO_FIN_EULER) | (last && (!forward_only || do_reset) ? MYO_FIN_STATE : 0) | (last ? MYO_FIN_WARM | MYO_FIN_ACC : 0);
+      static const bool fuse_finish = !(getenv("MYO_FUSE_FINISH") && atoi(getenv("MYO_FUSE_FINISH")) == 0);   // developer knob
+      ok &= tile(MYO_K_NEWTON, fslot, (forward_only ? 0 : 1) | (fuse_finish ? (fin << 1) | 32 : 0) | (b->D.nv << 8)) == 0;
       if (conout && conout_late) {
         ok &= cudaEventRecord(E(3), main) == cudaSuccess && cudaStreamWaitEvent(S(3), E(3), 0) == cudaSuccess;
         cur = b->side[3]; ok &= tile(MYO_K_CONOUT, fslot, 0) == 0; cur = stream;
-        ok &= cudaEventRecord(E(4), S(3)) == cudaSuccess;
       }
-      ok &= tile(MYO_K_FINISH, fslot, (forward_only ? 0 : MYO_FIN_EULER) | (last && (!forward_only || do_reset) ? MYO_FIN_STATE : 0) |
-                                          (last ? MYO_FIN_WARM | MYO_FIN_ACC : 0)) == 0;
-      if (conout) ok &= cudaStreamWaitEvent(main, E(4), 0) == cudaSuccess;
+      if (!fuse_finish) ok &= tile(MYO_K_FINISH, fslot, fin) == 0;
+      if (conout || posout) ok &= cudaEventRecord(E(4), S(3)) == cudaSuccess && cudaStreamWaitEvent(main, E(4), 0) == cudaSuccess;
       continue;
     }
+    if (posout) { ok &= tile(MYO_K_POSOUT, fslot, 0) == 0; STOP_HERE(); }
     ok &= tile(MYO_K_TENDON, fslot, 0) == 0; STOP_HERE();
     if (!posvel) {
       ok &= tile(MYO_K_INERTIA, fslot, forward_only ? 0 : 1) == 0; STOP_HERE();

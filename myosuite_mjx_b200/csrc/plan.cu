@@ -650,14 +650,11 @@ void myo_make_layout(DevModel& D, int nconmax_req, int njmax_req, SmemLayout& L)
   // running count of wrapped geom units
   L.uwpt = take(6 * D.ngunit); L.gpre = take(D.ngunit + 1);
   L.wantw = 0;
-  int base = o;
   // overlay A: tendon stage
   L.slots = take(6 * D.nslot); L.ulen = take(D.nunit); L.uwrap = take(D.nunit);
   L.upts = take(6 * D.nunit);   // the units' site positions, for the step kernel's own path-point writer   // tangent points / wrapped-unit prefix counts for the path-point outputs
+  L.tmpbody = take(13 * D.nbody);   // posoutKernel's body-level records (it runs beside the tendon stage: no overlay)
   int endA = o;
-  o = base;
-  L.tmpbody = take(13 * D.nbody);   // position-output stage only (before the tendon stage)
-  endA = std::max(endA, o);
   o = endA;   // no overlay: the tendon, inertia and collision phases of a step run concurrently on separate streams (api.cu)
   // region B: collision, constraints, solver
   L.cgpose = take(12 * D.ncg); L.cgshape = take(5 * D.ncg);   // cgshape: effective type, size[3], rbound (per-world overrides)

@@ -112,7 +112,14 @@ __global__ void __launch_bounds__(32 * MAXW, MINB_KIN) kinKernel(int slot, int f
   }
   kinematics(slot, sm, t);
   comPos(slot, sm, t);
-  if (fslot != MYO_NSLOT) writePositionOutputs(slot, fslot, sm, t, W);
+}
+// The position stage's output fields (xpos ... site_xmat, cinert, subtree_com): everything after kin waits for kin, so the
+// copies (4/5 of the old kin kernel's time) are their own launch on the low-priority output stream, beside the next phases.
+__global__ void __launch_bounds__(32 * MAXW, MINB_KIN) posoutKernel(int slot, int fslot, int nworld, const int* __restrict__ mask, float* __restrict__ scratch) {
+  Timeline tline(slot, MYO_K_POSOUT);
+  Ctx c = tileCtx(slot, nworld, mask, scratch);
+  if (!c.live) return;
+  writePositionOutputs(slot, fslot, c.sm, c.t, c.W);
 }
 
 // ------------------------------------------------------------------------------------------ tendon: mj_tendon (+ path points)
@@ -1053,92 +1060,13 @@ __device__ __noinline__ int newtonTile(int slot, SP sm, Tm t, const NewtonMem& M
 
 // Shared memory of a tile: Hessian (lower triangle), its factor's diagonal and six nv-vectors, [element][32 lanes].  When a
 // model's block does not fit (nv beyond ~55), the same kernel runs with everything in the world's scratch column.
-// mj_makeConstraint as its own launch: it needs the contacts and the velocity, not the smooth forces, so it runs on the
-// collision stream beside the tendon / actuation stages (models with tendon limits: after them, api.cu).
-__global__ void __launch_bounds__(32 * MAXW, MINB_NEWTON) makeconKernel(int slot, int nworld, const int* __restrict__ mask, float* __restrict__ scratch) {
-  const SmemLayout& L = tP[slot].L;
-  Timeline tline(slot, MYO_K_MAKECON);
-  Ctx c = tileCtx(slot, nworld, mask, scratch);
-  const unsigned lmask = __ballot_sync(0xffffffffu, c.live);
-  if (!c.live) return;
-  SP sm = c.sm; Tm t = c.t;
-  int status = __float_as_int(sm[L.wstate + WS_STATUS]);
-  const int ncon = __float_as_int(sm[L.counts]);
-  const int nconT = __reduce_max_sync(lmask, ncon);
-  const int nefc = makeConstraintTile(slot, sm, t, ncon, nconT, &status);
-  if (t.tl == 0) { sm[L.counts + 1] = __int_as_float(nefc); sm[L.wstate + WS_STATUS] = __int_as_float(status); }
-}
-static inline size_t newtonSmemFloats(int nv) { return (size_t)(TRI(nv) + 7 * nv) * 32; }
-#define NEWTON_SMEM_MAX (190 * 1024)   // + ~31 KB of static reduction / scan buffers <= 227 KB per CTA
-__global__ void __launch_bounds__(32 * MAXW, MINB_NEWTON) newtonKernel(int slot, int fslot, int nworld, const int* __restrict__ mask, int check_acc,
-                                                    int use_smem, float* __restrict__ scratch) {
-  const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
-  extern __shared__ float tileShared[];
-  __shared__ int sBad[32];
-  const int lane = threadIdx.x & 31;
-  Timeline tline(slot, MYO_K_NEWTON);
-  Ctx c = tileCtx(slot, nworld, mask, scratch);
-  const unsigned lmask = __ballot_sync(0xffffffffu, c.live);
-  if (!c.live) return;
-  SP sm = c.sm; Tm t = c.t;
-  const int nv = D.nv;
-  int status = __float_as_int(sm[L.wstate + WS_STATUS]);
-  const int ncon = __float_as_int(sm[L.counts]);
-  const int nconT = __reduce_max_sync(lmask, ncon);
-  if (t.tl == 0) sBad[lane] = 0;
-  long long* dbg = tP[slot].X.dbg; long long tlast = dbg ? clock64() : 0;
-  const int nefc = __float_as_int(sm[L.counts + 1]);   // rows: makeconKernel
-  const int nefcT = __reduce_max_sync(lmask, nefc);
-  int niter = 0;
-  if (nefcT == 0) {   // tile-uniform
-    TFOR(i, nv) { const float a = sm[L.qacc_smooth + i]; sm[L.qacc + i] = a; sm[L.warm + i] = a; sm[L.qfrc_con + i] = 0.f; }
-  } else {
-    NewtonMem M;
-    if (use_smem) {
-      float* p = tileShared + lane;
-      auto take = [&](int n) { SP r; r.p = p; p += n * SCR; return r; };
-      M.H = take(TRI(nv)); M.Hd = take(nv); M.qacc = take(nv); M.Ma = take(nv); M.grad = take(nv); M.search = take(nv); M.Mv = take(nv); M.tmp = take(nv);
-    } else {
-      M.H = sm + L.H; M.Hd = sm + L.H + TRI(nv); M.qacc = sm + L.nvec; M.Ma = M.qacc + nv; M.grad = M.Ma + nv; M.search = M.grad + nv;
-      M.Mv = M.search + nv; M.tmp = M.Mv + nv;
-    }
-    niter = newtonTile(slot, sm, t, M, lmask, ncon, nconT, nefc, &status);
-    // a world without rows in a tile that has some: its warm start and its only candidate coincide, qacc = qacc_smooth
-    TFOR(i, nv) { const float a = nefc > 0 ? M.qacc[i] : sm[L.qacc_smooth + i]; sm[L.qacc + i] = a; sm[L.warm + i] = a; if (nefc == 0) sm[L.qfrc_con + i] = 0.f; }
-  }
-  TSYNC();
-  // mj_checkAcc: a world whose qacc went bad is reset (qpos0, zero velocity / activation) and flagged; finishKernel does
-  // not integrate it, its next forward pass starts from the reset state.
-  int skip = 0;
-  if (check_acc) {
-    bool bad = false;
-    TFOR(i, nv) bad |= !(fabsf(sm[L.qacc + i]) < 1e10f);
-    if (bad) sBad[lane] = 1;
-    TSYNC();
-    if (sBad[lane]) {
-      TFOR(i, D.nq) sm[L.qpos + i] = D.qpos0[i];
-      TFOR(i, nv) { sm[L.qvel + i] = 0.f; sm[L.warm + i] = 0.f; }
-      TFOR(i, D.na) sm[L.act + i] = 0.f;
-      status |= MYO_WORLD_BADQACC; skip = 1;
-    }
-  }
-  if (fslot != MYO_NSLOT && D.nsensor > 0) touchSensors(slot, fslot, sm, t, c.W, nefc > 0 ? ncon : 0);
-  if (t.tl == 0) {
-    sm[L.counts + 2] = __int_as_float(niter);
-    sm[L.wstate + WS_STATUS] = __int_as_float(status); sm[L.wstate + WS_SKIP] = __int_as_float(skip);
-  }
-}
-
 // ------------------------------------------------------------------------------------------ finish: mj_Euler, state out
 // mj_Euler with implicit joint damping (the factor of M + h B comes from inertiaKernel), quaternion integration on the
 // manifold; then the state and the per-dof results of the solve go out as full lines.
-__global__ void __launch_bounds__(32 * MAXW, MINB_FINISH) finishKernel(int slot, int fslot, int nworld, const int* __restrict__ mask, int flags,
-                                                    float* __restrict__ scratch) {
+// (a device function: the solver kernel runs it as its own tail -- each tile goes on to integrate as soon as ITS solve is
+// done, instead of the whole batch meeting at a kernel boundary first; finishKernel remains for the paths without a solve)
+__device__ __noinline__ void finishTile(int slot, int fslot, SP sm, Tm t, World W, int flags) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L; const FieldPtrs& F = tP[slot].F;
-  Timeline tline(slot, MYO_K_FINISH);
-  Ctx c = tileCtx(slot, nworld, mask, scratch);
-  if (!c.live) return;
-  SP sm = c.sm; Tm t = c.t; World W = c.W;
   const int nq = D.nq, nv = D.nv, na = D.na, nu = D.nu;
   if (flags & FIN_ACC) {   // results of the solve (read-only here; mj_Euler below does not change them)
     const FieldPtrs& Fo = tP[fslot].F;
@@ -1203,6 +1131,93 @@ __global__ void __launch_bounds__(32 * MAXW, MINB_FINISH) finishKernel(int slot,
   void* gs = F.p[MYO_F_STATUS];
   if (gs && t.tl == 0) OUTI(gs, 0) = __float_as_int(sm[L.wstate + WS_STATUS]);
 }
+__global__ void __launch_bounds__(32 * MAXW, MINB_FINISH) finishKernel(int slot, int fslot, int nworld, const int* __restrict__ mask, int flags,
+                                                    float* __restrict__ scratch) {
+  Timeline tline(slot, MYO_K_FINISH);
+  Ctx c = tileCtx(slot, nworld, mask, scratch);
+  if (!c.live) return;
+  finishTile(slot, fslot, c.sm, c.t, c.W, flags);
+}
+
+// mj_makeConstraint as its own launch: it needs the contacts and the velocity, not the smooth forces, so it runs on the
+// collision stream beside the tendon / actuation stages (models with tendon limits: after them, api.cu).
+__global__ void __launch_bounds__(32 * MAXW, MINB_NEWTON) makeconKernel(int slot, int nworld, const int* __restrict__ mask, float* __restrict__ scratch) {
+  const SmemLayout& L = tP[slot].L;
+  Timeline tline(slot, MYO_K_MAKECON);
+  Ctx c = tileCtx(slot, nworld, mask, scratch);
+  const unsigned lmask = __ballot_sync(0xffffffffu, c.live);
+  if (!c.live) return;
+  SP sm = c.sm; Tm t = c.t;
+  int status = __float_as_int(sm[L.wstate + WS_STATUS]);
+  const int ncon = __float_as_int(sm[L.counts]);
+  const int nconT = __reduce_max_sync(lmask, ncon);
+  const int nefc = makeConstraintTile(slot, sm, t, ncon, nconT, &status);
+  if (t.tl == 0) { sm[L.counts + 1] = __int_as_float(nefc); sm[L.wstate + WS_STATUS] = __int_as_float(status); }
+}
+static inline size_t newtonSmemFloats(int nv) { return (size_t)(TRI(nv) + 7 * nv) * 32; }
+#define NEWTON_SMEM_MAX (190 * 1024)   // + ~31 KB of static reduction / scan buffers <= 227 KB per CTA
+__global__ void __launch_bounds__(32 * MAXW, MINB_NEWTON) newtonKernel(int slot, int fslot, int nworld, const int* __restrict__ mask, int check_acc,
+                                                    int use_smem, int fin, float* __restrict__ scratch) {
+  const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
+  extern __shared__ float tileShared[];
+  __shared__ int sBad[32];
+  const int lane = threadIdx.x & 31;
+  Timeline tline(slot, MYO_K_NEWTON);
+  Ctx c = tileCtx(slot, nworld, mask, scratch);
+  const unsigned lmask = __ballot_sync(0xffffffffu, c.live);
+  if (!c.live) return;
+  SP sm = c.sm; Tm t = c.t;
+  const int nv = D.nv;
+  int status = __float_as_int(sm[L.wstate + WS_STATUS]);
+  const int ncon = __float_as_int(sm[L.counts]);
+  const int nconT = __reduce_max_sync(lmask, ncon);
+  if (t.tl == 0) sBad[lane] = 0;
+  long long* dbg = tP[slot].X.dbg; long long tlast = dbg ? clock64() : 0;
+  const int nefc = __float_as_int(sm[L.counts + 1]);   // rows: makeconKernel
+  const int nefcT = __reduce_max_sync(lmask, nefc);
+  int niter = 0;
+  if (nefcT == 0) {   // tile-uniform
+    TFOR(i, nv) { const float a = sm[L.qacc_smooth + i]; sm[L.qacc + i] = a; sm[L.warm + i] = a; sm[L.qfrc_con + i] = 0.f; }
+  } else {
+    NewtonMem M;
+    if (use_smem) {
+      float* p = tileShared + lane;
+      auto take = [&](int n) { SP r; r.p = p; p += n * SCR; return r; };
+      M.H = take(TRI(nv)); M.Hd = take(nv); M.qacc = take(nv); M.Ma = take(nv); M.grad = take(nv); M.search = take(nv); M.Mv = take(nv); M.tmp = take(nv);
+    } else {
+      M.H = sm + L.H; M.Hd = sm + L.H + TRI(nv); M.qacc = sm + L.nvec; M.Ma = M.qacc + nv; M.grad = M.Ma + nv; M.search = M.grad + nv;
+      M.Mv = M.search + nv; M.tmp = M.Mv + nv;
+    }
+    niter = newtonTile(slot, sm, t, M, lmask, ncon, nconT, nefc, &status);
+    // a world without rows in a tile that has some: its warm start and its only candidate coincide, qacc = qacc_smooth
+    TFOR(i, nv) { const float a = nefc > 0 ? M.qacc[i] : sm[L.qacc_smooth + i]; sm[L.qacc + i] = a; sm[L.warm + i] = a; if (nefc == 0) sm[L.qfrc_con + i] = 0.f; }
+  }
+  TSYNC();
+  // mj_checkAcc: a world whose qacc went bad is reset (qpos0, zero velocity / activation) and flagged; finishKernel does
+  // not integrate it, its next forward pass starts from the reset state.
+  int skip = 0;
+  if (check_acc) {
+    bool bad = false;
+    TFOR(i, nv) bad |= !(fabsf(sm[L.qacc + i]) < 1e10f);
+    if (bad) sBad[lane] = 1;
+    TSYNC();
+    if (sBad[lane]) {
+      TFOR(i, D.nq) sm[L.qpos + i] = D.qpos0[i];
+      TFOR(i, nv) { sm[L.qvel + i] = 0.f; sm[L.warm + i] = 0.f; }
+      TFOR(i, D.na) sm[L.act + i] = 0.f;
+      status |= MYO_WORLD_BADQACC; skip = 1;
+    }
+  }
+  if (fslot != MYO_NSLOT && D.nsensor > 0) touchSensors(slot, fslot, sm, t, c.W, nefc > 0 ? ncon : 0);
+  if (t.tl == 0) {
+    sm[L.counts + 2] = __int_as_float(niter);
+    sm[L.wstate + WS_STATUS] = __int_as_float(status); sm[L.wstate + WS_SKIP] = __int_as_float(skip);
+  }
+  if (fin >= 0) {   // mj_Euler and the state / result outputs of this tile (finishTile)
+    TSYNC();
+    finishTile(slot, fslot, sm, t, c.W, fin);
+  }
+}
 
 // ------------------------------------------------------------------------------------------ conout: contact / constraint records
 // contact_* and efc_* (padded to nconmax / njmax, efc_J expanded to dense rows): pure stores, no ordering between items, so
@@ -1254,7 +1269,7 @@ int myo_tile_launch(int kernel, int slot, int fslot, int nworld, const int* mask
   // solver (8: +6.6 % step time, 10: +3.9 %, 16 at <= 64 registers: +1.8 %); the tendon phase prefers 8.
   static const int nwKin = envInt("MYO_NW_KIN", 12), nwTen = envInt("MYO_NW_TEN", 8), nwIne = envInt("MYO_NW_INE", 8),
                    nwCol = envInt("MYO_NW_COL", 12), nwVel = envInt("MYO_NW_VEL", 12), nwFin = envInt("MYO_NW_FIN", 8),
-                   nwOut = envInt("MYO_NW_OUT", 8), yOut = envInt("MYO_Y_OUT", 4), nwNew = envInt("MYO_NW_NEWTON", 12), nwMak = envInt("MYO_NW_MAKECON", 12);
+                   nwOut = envInt("MYO_NW_OUT", 8), yOut = envInt("MYO_Y_OUT", 4), nwNew = envInt("MYO_NW_NEWTON", 12), nwMak = envInt("MYO_NW_MAKECON", 12), nwPos = envInt("MYO_NW_POSOUT", 8);
   const int tiles = (nworld + 31) / 32;
   cudaStream_t st = (cudaStream_t)stream;
   switch (kernel) {
@@ -1280,8 +1295,9 @@ int myo_tile_launch(int kernel, int slot, int fslot, int nworld, const int* mask
           configured[dev] = shmem;
         }
       }
-      newtonKernel<<<tiles, 32 * nwNew, shmem, st>>>(slot, fslot, nworld, mask, flags & 1, use_smem, scratch);
+      newtonKernel<<<tiles, 32 * nwNew, shmem, st>>>(slot, fslot, nworld, mask, flags & 1, use_smem, (flags & 32) ? ((flags >> 1) & 15) : -1, scratch);
     } break;
+    case MYO_K_POSOUT: posoutKernel<<<tiles, 32 * nwPos, 0, st>>>(slot, fslot, nworld, mask, scratch); break;
     case MYO_K_MAKECON: makeconKernel<<<tiles, 32 * nwMak, 0, st>>>(slot, nworld, mask, scratch); break;
     case MYO_K_CONOUT: conoutKernel<<<dim3(tiles, yOut), 32 * nwOut, 0, st>>>(slot, fslot, nworld, mask, scratch); break;
     default: return -1;

@@ -9,7 +9,7 @@ from myosuite_mjx_b200 import mjx, lib, partition
 m = bench.load_model("hand")
 model = mjx.put_model(m)
 nw = 8192
-d = mjx.put_data(model, dict(qpos=bench.initial_qpos(m, nw, 1234)), nworld=nw, fields="all")
+d = mjx.put_data(model, dict(qpos=bench.initial_qpos(m, nw, 1234)), nworld=nw, fields=os.environ.get("FIELDS", "all"))
 L = lib.lib()
 A, N = (int(sys.argv[1]), int(sys.argv[2])) if len(sys.argv) > 2 else (300, 20)
 def run(n0, n1):
@@ -17,7 +17,7 @@ def run(n0, n1):
         if i % 10 == 0: d.storage("ctrl").copy_(partition.ctrl_hash_torch(m.nu, 0, nw, 1234, i // 10, "cuda"))
         mjx.step(model, d, 1)
 run(0, A)
-names = ["kin", "tendon", "inertia", "collide", "velact", "finish", "conout", "newton", "collideMpr", "collideCompact", "makecon"]
+names = ["kin", "tendon", "inertia", "collide", "velact", "finish", "conout", "newton", "collideMpr", "collideCompact", "makecon", "posout"]
 buf = (ctypes.c_ulonglong * 64)()
 L.myo_debug_timeline(d._h, buf)
 acc = np.zeros((len(names), 2)); tot = 0.0
