@@ -224,9 +224,12 @@ static int clearPathPoints(myo_batch* b, void* stream) {
   return MYO_OK;
 }
 
-// The phase pipeline: one mj_step = kin -> tendon -> inertia -> collide -> velact -> newton -> conout -> finish (tile.cu, lane =
-// world).  All launches go to the caller's stream, in order; every mjData field is written by the phase that produces it,
-// as full lines; inner substeps of a fused launch materialise nothing.
+// The phase pipeline (tile.cu, lane = world): one mj_step = kin, then  collide > collideMpr > collideCompact > makecon  |
+// tendon > velact  |  inertia  on three library streams, the output fields of the position stage (posout) and the contact /
+// constraint records (conout) on a fourth, low-priority one; all join before newton on the caller's stream, whose tail is
+// mj_Euler and the state outputs.  Everything is ordered behind the caller's stream on entry and joined into it on exit, so
+// the call is stream-ordered like a single kernel.  MYO_CONCURRENT=0 (developer knob) or a partial pass (posvel) runs
+// the same kernels in order on the caller's stream.  Inner substeps of a fused launch materialise nothing.
 static int launchPhases(myo_batch* b, int nsub, int forward_only, const int32_t* mask, int do_reset, void* stream) {
   int rc;
   if (b->dirty) {

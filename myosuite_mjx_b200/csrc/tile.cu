@@ -9,23 +9,27 @@
 // The collision phase keeps per-lane candidate lists and compacts in order by per-warp chunks; the constraint solve runs the
 // tile's 32 worlds in lock step (per-lane activity masks).
 //
-// One mj_step = kin -> tendon -> inertia -> collide -> velact -> newton -> conout -> finish   (api.cu).
+// One mj_step (api.cu launchPhases): kin, then three branches on their own streams --
+//   collide -> collideMpr -> collideCompact -> makecon   |   tendon -> velact   |   inertia (+ body velocities, bias force)
+// -- plus the output stream (posout after kin, conout after makecon), then newton, whose tail is mj_Euler + the state outputs.
+// Measured (profiles/r2f_*): every kernel is bound by the latency of its dependent instructions, and the register file holds
+// at most two or three kernels' tiles at once, so the phase-2 kernels are capped at 56 registers (three CTAs per SM).
 #include "common.cuh"
 
 #ifndef MINB_KIN
 #define MINB_KIN 2
 #endif
 #ifndef MINB_TENDON
-#define MINB_TENDON 2
+#define MINB_TENDON 3
 #endif
 #ifndef MINB_INERTIA
-#define MINB_INERTIA 2
+#define MINB_INERTIA 3
 #endif
 #ifndef MINB_VELACT
-#define MINB_VELACT 2
+#define MINB_VELACT 3
 #endif
 #ifndef MINB_COLLIDE
-#define MINB_COLLIDE 2
+#define MINB_COLLIDE 3
 #endif
 #ifndef MINB_NEWTON
 #define MINB_NEWTON 2
@@ -115,7 +119,10 @@ __global__ void __launch_bounds__(32 * MAXW, MINB_KIN) kinKernel(int slot, int f
 }
 // The position stage's output fields (xpos ... site_xmat, cinert, subtree_com): everything after kin waits for kin, so the
 // copies (4/5 of the old kin kernel's time) are their own launch on the low-priority output stream, beside the next phases.
-__global__ void __launch_bounds__(32 * MAXW, MINB_KIN) posoutKernel(int slot, int fslot, int nworld, const int* __restrict__ mask, float* __restrict__ scratch) {
+#ifndef MINB_POSOUT
+#define MINB_POSOUT 3
+#endif
+__global__ void __launch_bounds__(32 * MAXW, MINB_POSOUT) posoutKernel(int slot, int fslot, int nworld, const int* __restrict__ mask, float* __restrict__ scratch) {
   Timeline tline(slot, MYO_K_POSOUT);
   Ctx c = tileCtx(slot, nworld, mask, scratch);
   if (!c.live) return;
@@ -1141,7 +1148,10 @@ __global__ void __launch_bounds__(32 * MAXW, MINB_FINISH) finishKernel(int slot,
 
 // mj_makeConstraint as its own launch: it needs the contacts and the velocity, not the smooth forces, so it runs on the
 // collision stream beside the tendon / actuation stages (models with tendon limits: after them, api.cu).
-__global__ void __launch_bounds__(32 * MAXW, MINB_NEWTON) makeconKernel(int slot, int nworld, const int* __restrict__ mask, float* __restrict__ scratch) {
+#ifndef MINB_MAKECON
+#define MINB_MAKECON 3
+#endif
+__global__ void __launch_bounds__(32 * MAXW, MINB_MAKECON) makeconKernel(int slot, int nworld, const int* __restrict__ mask, float* __restrict__ scratch) {
   const SmemLayout& L = tP[slot].L;
   Timeline tline(slot, MYO_K_MAKECON);
   Ctx c = tileCtx(slot, nworld, mask, scratch);
