@@ -364,6 +364,24 @@ int myo_env_forward(myo_env *e, void *cuda_stream);
  * rotated [n,3] = mat * qb[1:4]. */
 int myo_kat_quat(int n, const float *qa, const float *qb, float *prod, float *mat, float *rotated, void *cuda_stream);
 
+/* Allocation-free forward kinematics.  NO COUNTERPART IN THE REFERENCE: added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Runs mj_kinematics + mj_comPos of `nworld` worlds of model `m` from `qpos` and writes the requested position-stage
+ * outputs -- the same arithmetic, in the same order, as myo_forward on a batch (the kin + posout kernels fused into one
+ * launch), so the results are bit-identical to the xpos / xquat / xmat / site_xpos / geom_xpos fields of a batch.
+ *   qpos      [nq][nworld]        device, float32, world axis fastest (the layout of every field above)
+ *   xpos      [3 nbody][nworld]   device or NULL      xquat [4 nbody][nworld] or NULL      xmat [9 nbody][nworld] or NULL
+ *   site_xpos [3 nsite][nworld]   device or NULL      geom_xpos [3 ngeom][nworld] or NULL  (at least one output)
+ * The call itself allocates nothing (no cudaMalloc / cudaFree, no allocating library routine): the per-world scratch a
+ * batch would own lives in one fixed 8 MiB device array inside the library, which every GPU that loads the library holds
+ * until exit.  LIMIT: ceil(nworld / 32) * scratch floats per 32-world tile * 128 B <= 8 MiB (MyoHand: about 1300 worlds);
+ * a larger nworld is rejected with MYO_ERR_ARG and a message that states the model's maximum.  The model itself was
+ * allocated by myo_model_create, before.  Enqueued on `cuda_stream` (a memset of the scratch in use, the parameter upload,
+ * one kernel); no synchronisation.  All calls share the array and one parameter slot: host-side calls are serialised by a
+ * mutex, but calls that OVERLAP ON THE GPU (different streams, no ordering between them) race -- order them. */
+int myo_kinematics_noalloc(const myo_model *m, int nworld, const float *qpos, float *xpos, float *xquat, float *xmat,
+                           float *site_xpos, float *geom_xpos, void *cuda_stream);
+
 /* number of kernels launched by this library since load (for bench.py's gpu_launches) */
 int64_t myo_launch_count(void);
 

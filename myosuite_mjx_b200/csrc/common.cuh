@@ -29,8 +29,9 @@
 #define TEAM (t.nw)   // item stride of a loop = the NW warps of the tile's CTA (NW = blockDim.x / 32, a launch parameter)
 struct TParams { DevModel D; SmemLayout L; FieldPtrs F; TileAux X; };
 #define MYO_NSLOT MYO_PARAM_SLOTS
-static_assert(sizeof(TParams) * (MYO_NSLOT + 1) <= 60 * 1024, "parameter slots exceed constant memory");
-__constant__ TParams tP[MYO_NSLOT + 1];   // slot MYO_NSLOT stays zero: "materialise nothing" (inner substeps)
+#define MYO_NOALLOC_SLOT (MYO_NSLOT + 1)   // parameters of myo_kinematics_noalloc (tile.cu): no batch, so no batch slot
+static_assert(sizeof(TParams) * (MYO_NSLOT + 2) <= 60 * 1024, "parameter slots exceed constant memory");
+__constant__ TParams tP[MYO_NSLOT + 2];   // slot MYO_NSLOT stays zero: "materialise nothing" (inner substeps)
 namespace {
 
 enum { JNT_FREE = 0, JNT_BALL = 1, JNT_SLIDE = 2, JNT_HINGE = 3 };

@@ -15,6 +15,9 @@
 // Measured (profiles/r2f_*): every kernel is bound by the latency of its dependent instructions, and the register file holds
 // at most two or three kernels' tiles at once, so the phase-2 kernels are capped at 56 registers (three CTAs per SM).
 #include "common.cuh"
+#include <cstring>
+#include <mutex>
+#include <string>
 
 #ifndef MINB_KIN
 #define MINB_KIN 2
@@ -1317,4 +1320,67 @@ int myo_tile_launch(int kernel, int slot, int fslot, int nworld, const int* mask
 int myo_launch_quat_kat(int n, const float* qa, const float* qb, float* prod, float* mat, float* rotated, void* stream) {
   quatKatKernel<<<(n + 127) / 128, 128, 0, (cudaStream_t)stream>>>(n, qa, qb, prod, mat, rotated);
   return cudaPeekAtLastError() == cudaSuccess ? 0 : -1;
+}
+
+// ---------------------------------------------------------------------------------------------- allocation-free entry point
+// myo_kinematics_noalloc (include/myostep.h): mj_kinematics + mj_comPos and the position-stage outputs for callers that
+// cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).  No counterpart in the
+// reference.  The kernel is the kin + posout pair of the pipeline fused into
+// one launch; its per-world scratch (the front of the pipeline's layout: state, frames, anchors, axes, tree centres of mass,
+// body inertias, cdof, + the body-level records of the output stage) lives in a file-scope device array of fixed size
+// instead of a batch's cudaMalloc'ed buffer.  Every GPU that loads the library holds the array until exit; all calls share
+// it, so calls that overlap on the GPU race (see the header).
+#define MYO_NOALLOC_SCRATCH_BYTES (8u << 20)
+namespace {
+static __device__ __align__(256) float g_noallocScratch[MYO_NOALLOC_SCRATCH_BYTES / sizeof(float)];
+__global__ void __launch_bounds__(32 * MAXW, 2) kinNoallocKernel(int slot, int nworld, const float* __restrict__ qpos, float* __restrict__ scratch) {
+  const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
+  Ctx c = tileCtx(slot, nworld, nullptr, scratch);
+  if (!c.live) return;
+  SP sm = c.sm; Tm t = c.t; World W = c.W;
+  TFOR(i, D.nq) sm[L.qpos + i] = OUTF(qpos, i);
+  TSYNC();
+  kinematics(slot, sm, t);
+  comPos(slot, sm, t);
+  writePositionOutputs(slot, slot, sm, t, W);
+}
+std::mutex g_noallocMutex;          // one parameter slot and one scratch array: host-side calls are serialised
+float* g_noallocPtr[64] = {nullptr};  // device address of g_noallocScratch, per device (the symbol's name is only a host-side stand-in)
+TParams g_noallocParams;            // staging of the parameter upload (outlives the asynchronous copy)
+}  // namespace
+
+int myo_kinematics_noalloc(const myo_model* m, int nworld, const float* qpos, float* xpos, float* xquat, float* xmat,
+                           float* site_xpos, float* geom_xpos, void* stream) {
+  if (!m || !qpos || nworld <= 0) return myo_fail(MYO_ERR_ARG, "myo_kinematics_noalloc: null model / qpos or nworld <= 0");
+  if (!xpos && !xquat && !xmat && !site_xpos && !geom_xpos) return myo_fail(MYO_ERR_ARG, "myo_kinematics_noalloc: no output buffer given");
+  if (m->device < 0 || m->device >= 64) return myo_fail(MYO_ERR_ARG, "myo_kinematics_noalloc: device index out of range");
+  if (cudaSetDevice(m->device) != cudaSuccess) return myo_fail(MYO_ERR_CUDA, "cudaSetDevice failed");
+  std::lock_guard<std::mutex> lk(g_noallocMutex);
+  // the pipeline's layout, cut after the regions this stage touches (everything before cdof_dot), + the output stage's records
+  TParams& P = g_noallocParams;
+  memset(&P, 0, sizeof(P));
+  P.D = m->D;
+  try { myo_make_layout(P.D, 0, 0, P.L); } catch (const std::string& e) { return myo_fail(MYO_ERR_ARG, e); }
+  P.L.tmpbody = P.L.cdof_dot;
+  P.L.total = P.L.tmpbody + ((13 * P.D.nbody + 3) & ~3);
+  const size_t tiles = ((size_t)nworld + 31) / 32, tileBytes = (size_t)P.L.total * 32 * sizeof(float);
+  if (tiles * tileBytes > MYO_NOALLOC_SCRATCH_BYTES)
+    return myo_fail(MYO_ERR_ARG, "myo_kinematics_noalloc: nworld " + std::to_string(nworld) + " exceeds the fixed scratch (8 MiB = " +
+                                     std::to_string(MYO_NOALLOC_SCRATCH_BYTES / tileBytes * 32) + " worlds of this model); use a batch (myo_batch_create + myo_forward)");
+  float*& ptr = g_noallocPtr[m->device];
+  if (!ptr) {   // once per device, with that device current
+    void* p = nullptr;
+    if (cudaGetSymbolAddress(&p, g_noallocScratch) != cudaSuccess || !p) return myo_fail(MYO_ERR_CUDA, std::string("cudaGetSymbolAddress failed: ") + cudaGetErrorString(cudaGetLastError()));
+    ptr = (float*)p;
+  }
+  P.F.p[MYO_F_XPOS] = xpos; P.F.p[MYO_F_XQUAT] = xquat; P.F.p[MYO_F_XMAT] = xmat; P.F.p[MYO_F_SITE_XPOS] = site_xpos; P.F.p[MYO_F_GEOM_XPOS] = geom_xpos;
+  cudaStream_t st = (cudaStream_t)stream;
+  // the array keeps the last call's contents: the part this call uses starts from zeros, like a batch's scratch
+  if (cudaMemsetAsync(ptr, 0, tiles * tileBytes, st) != cudaSuccess) return myo_fail(MYO_ERR_CUDA, "cudaMemsetAsync failed");
+  if (cudaMemcpyToSymbolAsync(tP, &P, sizeof(TParams), (size_t)MYO_NOALLOC_SLOT * sizeof(TParams), cudaMemcpyHostToDevice, st) != cudaSuccess)
+    return myo_fail(MYO_ERR_CUDA, "parameter upload failed");
+  myo_count_launch(1);
+  kinNoallocKernel<<<(unsigned)tiles, 32 * 8, 0, st>>>(MYO_NOALLOC_SLOT, nworld, qpos, ptr);
+  if (cudaPeekAtLastError() != cudaSuccess) return myo_fail(MYO_ERR_CUDA, std::string("kernel launch failed: ") + cudaGetErrorString(cudaGetLastError()));
+  return MYO_OK;
 }
