@@ -87,7 +87,11 @@ enum {
   MYO_ERR_UNBOUND = -4       /* a required state field has no bound device buffer */
 };
 
-/* per-world status bits written by the step kernel into the `status` field */
+/* per-world status bits written by the step kernels into the `status` field.
+ * DEVIATION from MuJoCo, on purpose: mj_checkPos / mj_checkVel / mj_checkAcc call mj_resetData (qpos0, zero qvel / act / ctrl,
+ * time = 0, a warning counter) and carry on; here the bad world is reset to qpos0 with zero qvel / act / warm start, its `time`
+ * and `ctrl` are KEPT (the batch shares one control loop), it is not integrated on the step that found the bad qacc, and the
+ * event is recorded as a bit in `status` (sticky until the caller clears the field) instead of mjData.warning. */
 enum {
   MYO_WORLD_BADQACC = 1,     /* NaN/Inf or huge qacc: world was reset to qpos0 (mj_checkAcc rule) */
   MYO_WORLD_NCON_OVERFLOW = 2,
