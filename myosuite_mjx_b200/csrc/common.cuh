@@ -1223,7 +1223,7 @@ __device__ __noinline__ void resetState(int slot, SP sm, Tm t) {
 }
 
 // ------------------------------------------------------------------------------------------ constraint rows (shared record layout)
-// Rows are never stored densely: a row is (type, id, coef) and its Jacobian is implied (team.cu "constraints").
+// Rows are never stored densely: a row is (type, id, coef) and its Jacobian is implied (limit rows 1-sparse, equality rows 2-sparse, tendon-limit rows the tendon's sparse row, contact rows +- base rows).
 enum { E_D = 0, E_AREF, E_JAR, E_JV, E_FORCE, E_DESC0, E_COEF, E_DESC1, E_POS, E_MARGIN };
 #define EFC(k, r) sm[L.efc + (k) * D.njmax + (r)]
 #define EFCI(k, r) __float_as_int(sm[L.efc + (k) * D.njmax + (r)])

@@ -881,7 +881,7 @@ __device__ __noinline__ void cholSolveTile(int nv, SP H, SP Hd, SP x, SP y, Tm t
     TSYNC();
   }
 }
-// K points of the 1-D cost along the search direction in one pass over the lane's rows (see team.cu lsEval for `tol`)
+// K points of the 1-D cost along the search direction in one pass over the lane's rows (`tol`: the float32 noise floor of the derivative test, LS_NOISE)
 #ifndef LS_NOISE
 #define LS_NOISE 2e-6f
 #endif
