@@ -136,6 +136,12 @@ struct SP {
 #else
 #define LDJ(ref) (ref)
 #endif
+// the same choice for the sweeps that read each element once (J x, J^T f, U = W Jb) and gain nothing from L1
+#ifndef NO_STREAM_SWEEPS
+#define LDJS(ref) __ldcg(&(ref))   // -0.5 % step time (two A/B runs)
+#else
+#define LDJS(ref) LDJ(ref)
+#endif
 struct SPI {
   int* p;
   __device__ __forceinline__ int& operator[](int i) const { return p[i * SCR]; }
@@ -1345,24 +1351,41 @@ __device__ __noinline__ void setRow(int slot, SP sm, int r, int type, int id, fl
   EFC(E_POS, r) = pos; EFC(E_MARGIN, r) = margin; EFC(E_FORCE, r) = 0.f;
 }
 // base-row products  out[b] = conJ[b] . x   for the nb*ncon contact base rows
-__device__ __noinline__ void baseMul(int slot, SP sm, Tm t, int ncon, SP x, SP out) {
+// out[n] = Jb x[n] for NX right-hand sides in one sweep over the base rows.  Two rows per pass; the loads of a chunk of JKB
+// columns of both rows are issued before the first use (the dot products are bound by the latency of the J loads, which
+// miss L1: ~16 of them in flight per warp instead of 4).  Even / odd columns keep separate accumulators (summation order
+// as before the chunking).
+#ifndef JKB
+#define JKB 8
+#endif
+template <int NX> __device__ __forceinline__ void baseMulT(int slot, SP sm, Tm t, int ncon, const SP* x, const SP* out) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
   const int nbr = D.maxbase * ncon, nv = D.nv;
-  // two rows per pass (they share the loads of x), two accumulators each: the dot products are latency-bound
   for (int b = t.tl; b < nbr; b += 2 * TEAM) {
     const int b2 = b + TEAM;
     auto J0 = sm + L.conJ + b * nv; auto J1 = sm + L.conJ + min(b2, nbr - 1) * nv;
-    float a0 = 0.f, a1 = 0.f, c0 = 0.f, c1 = 0.f;
-    int k = 0;
-    HOT
-    for (; k + 1 < nv; k += 2) {
-      const float x0 = x[k], x1 = x[k + 1];
-      a0 = fmaf(LDJ(J0[k]), x0, a0); a1 = fmaf(LDJ(J0[k + 1]), x1, a1); c0 = fmaf(LDJ(J1[k]), x0, c0); c1 = fmaf(LDJ(J1[k + 1]), x1, c1);
+    float a[NX][2], c[NX][2];
+#pragma unroll
+    for (int n = 0; n < NX; n++) { a[n][0] = a[n][1] = c[n][0] = c[n][1] = 0.f; }
+    for (int k0 = 0; k0 < nv; k0 += JKB) {
+      float j0[JKB], j1[JKB];
+#pragma unroll
+      for (int i = 0; i < JKB; i++) { j0[i] = LDJS(J0[k0 + i]); j1[i] = LDJS(J1[k0 + i]); }   // (past the row end: the next row or region of the scratch, masked below)
+#pragma unroll
+      for (int i = 0; i < JKB; i++)
+        if (k0 + i < nv) {
+#pragma unroll
+          for (int n = 0; n < NX; n++) { const float xv = x[n][k0 + i]; a[n][i & 1] = fmaf(j0[i], xv, a[n][i & 1]); c[n][i & 1] = fmaf(j1[i], xv, c[n][i & 1]); }
+        }
     }
-    if (k < nv) { const float x0 = x[k]; a0 = fmaf(LDJ(J0[k]), x0, a0); c0 = fmaf(LDJ(J1[k]), x0, c0); }
-    out[b] = a0 + a1;
-    if (b2 < nbr) out[b2] = c0 + c1;
+#pragma unroll
+    for (int n = 0; n < NX; n++) { out[n][b] = a[n][0] + a[n][1]; if (b2 < nbr) out[n][b2] = c[n][0] + c[n][1]; }
   }
+}
+__device__ __noinline__ void baseMul(int slot, SP sm, Tm t, int ncon, SP x, SP out) { baseMulT<1>(slot, sm, t, ncon, &x, &out); }
+__device__ __noinline__ void baseMul2(int slot, SP sm, Tm t, int ncon, SP x0, SP x1, SP out0, SP out1) {
+  const SP x[2] = {x0, x1}; const SP out[2] = {out0, out1};
+  baseMulT<2>(slot, sm, t, ncon, x, out);
 }
 // J_r . x for one efc row (bx = base products of x)
 __device__ __forceinline__ float rowMul(int slot, SP sm, int r, SP x, SP bx) {
@@ -1407,6 +1430,83 @@ __device__ __noinline__ float residualCost(int slot, SP sm, Tm t, int ncon, int 
   TSYNC();
   return TSUM(cost);
 }
+// The two warm-start candidates in one sweep over J and the rows: cost[0] of x0 (rows not kept), cost[1] of x1, whose row
+// residuals stay in E_JAR.
+__device__ __noinline__ void residualCost2(int slot, SP sm, Tm t, int ncon, int nefc, SP x0, SP x1, float* cost) {
+  const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
+  auto bx0 = sm + L.basev + D.maxbase * D.nconmax; auto bx1 = sm + L.basev;   // (the base-force half of basev is free before the first force evaluation)
+  baseMul2(slot, sm, t, ncon, x0, x1, bx0, bx1);
+  TSYNC();
+  float c[2] = {0.f, 0.f};
+  TFOR(r, nefc) {
+    const float aref = EFC(E_AREF, r), Dr = EFC(E_D, r);
+    const int d0 = EFCI(E_DESC0, r);
+    const float jar0 = rowMul(slot, sm, r, x0, bx0) - aref, jar1 = rowMul(slot, sm, r, x1, bx1) - aref;
+    EFC(E_JAR, r) = jar1;
+    if (rowOn(d0, jar0)) c[0] = fmaf(0.5f * Dr * jar0, jar0, c[0]);
+    if (rowOn(d0, jar1)) c[1] = fmaf(0.5f * Dr * jar1, jar1, c[1]);
+  }
+  TSYNC();
+  cost[0] = TSUM(c[0]); cost[1] = TSUM(c[1]);
+}
+// the non-contact part of (J^T f)[k]: equality, joint-limit and tendon-limit rows that touch dof k
+__device__ __forceinline__ float sparseRowForce(int slot, SP sm, int k) {
+  const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
+  float acc = 0.f;
+  for (int e = D.dofeq_start[k]; e < D.dofeq_start[k + 1]; e++) {
+    const int v = D.dofeq_list[e], r = v >> 1;
+    acc += (v & 1) ? EFC(E_COEF, r) * EFC(E_FORCE, r) : EFC(E_FORCE, r);
+  }
+  const int li = D.dof_limidx[k];
+  if (li >= 0)
+    for (int q = 0; q < 2; q++) { const int r = __float_as_int(sm[L.limrow + 2 * li + q]); if (r >= 0) acc += EFC(E_COEF, r) * EFC(E_FORCE, r); }
+  if (D.nlimt > 0)
+    for (int c = D.col_start[k]; c < D.col_start[k + 1]; c++) {
+      const int n = D.col_nz[c], lt = D.ten_limidx[D.nz_tendon[n]];
+      if (lt < 0) continue;
+      for (int q = 0; q < 2; q++) {
+        const int r = __float_as_int(sm[L.limrow + 2 * (D.nlimj + lt) + q]);
+        if (r >= 0) acc += EFC(E_COEF, r) * EFC(E_FORCE, r) * sm[L.tenJ + n];
+      }
+    }
+  return acc;
+}
+// out = sparse rows + Jb^T bf: G dofs per warp and pass (they share the loads of bf), the J loads of four base rows issued
+// before their first use; even / odd base rows keep separate accumulators.  G = 2 when two passes' worth of warps cover nv
+// (a third dof would be a clamped duplicate: a third of the loads wasted at nv = 23, 12 warps).
+#ifndef JTB
+#define JTB 4
+#endif
+template <int G> __device__ __forceinline__ void jtForce(int slot, SP sm, Tm t, int nbr, SP bf, SP out) {
+  const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
+  const int nv = D.nv;
+  for (int kb = t.tl; kb < nv; kb += G * TEAM) {
+    float res[G]; int kk[G];
+#pragma unroll
+    for (int g = 0; g < G; g++) { const int k = kb + g * TEAM; kk[g] = min(k, nv - 1); res[g] = k < nv ? sparseRowForce(slot, sm, k) : 0.f; }
+    auto Jk = sm + L.conJ;
+    float a[G][2];
+#pragma unroll
+    for (int g = 0; g < G; g++) a[g][0] = a[g][1] = 0.f;
+    for (int b0 = 0; b0 < nbr; b0 += JTB) {
+      float j[JTB][G], f[JTB];
+#pragma unroll
+      for (int i = 0; i < JTB; i++) {   // (rows past nbr: other rows / the next region of the scratch, masked below)
+        f[i] = bf[b0 + i];
+#pragma unroll
+        for (int g = 0; g < G; g++) j[i][g] = LDJS(Jk[(b0 + i) * nv + kk[g]]);
+      }
+#pragma unroll
+      for (int i = 0; i < JTB; i++)
+        if (b0 + i < nbr) {
+#pragma unroll
+          for (int g = 0; g < G; g++) a[g][i & 1] = fmaf(j[i][g], f[i], a[g][i & 1]);
+        }
+    }
+#pragma unroll
+    for (int g = 0; g < G; g++) if (kb + g * TEAM < nv) out[kb + g * TEAM] = res[g] + a[g][0] + a[g][1];
+  }
+}
 // forces from jar, then out = J^T f  (deterministic gathers, no atomics)
 __device__ __noinline__ void constraintForce(int slot, SP sm, Tm t, int ncon, int nefc, SP out) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
@@ -1430,47 +1530,7 @@ __device__ __noinline__ void constraintForce(int slot, SP sm, Tm t, int ncon, in
   }
   TSYNC();
   const int nbr = nb * ncon;
-  for (int kb = t.tl; kb < nv; kb += 3 * TEAM) {   // three dofs per pass: they share the loads of bf
-    float res[3];
-    for (int g = 0; g < 3; g++) {
-      const int k = kb + g * TEAM;
-      float acc = 0.f;
-      if (k < nv) {
-        for (int e = D.dofeq_start[k]; e < D.dofeq_start[k + 1]; e++) {
-          const int v = D.dofeq_list[e], r = v >> 1;
-          acc += (v & 1) ? EFC(E_COEF, r) * EFC(E_FORCE, r) : EFC(E_FORCE, r);
-        }
-        const int li = D.dof_limidx[k];
-        if (li >= 0)
-          for (int q = 0; q < 2; q++) { const int r = __float_as_int(sm[L.limrow + 2 * li + q]); if (r >= 0) acc += EFC(E_COEF, r) * EFC(E_FORCE, r); }
-        if (D.nlimt > 0)
-          for (int c = D.col_start[k]; c < D.col_start[k + 1]; c++) {
-            const int n = D.col_nz[c], lt = D.ten_limidx[D.nz_tendon[n]];
-            if (lt < 0) continue;
-            for (int q = 0; q < 2; q++) {
-              const int r = __float_as_int(sm[L.limrow + 2 * (D.nlimj + lt) + q]);
-              if (r >= 0) acc += EFC(E_COEF, r) * EFC(E_FORCE, r) * sm[L.tenJ + n];
-            }
-          }
-      }
-      res[g] = acc;
-    }
-    const int k0 = kb, k1 = min(kb + TEAM, nv - 1), k2 = min(kb + 2 * TEAM, nv - 1);
-    auto Jk = sm + L.conJ;
-    float a0 = 0.f, a1 = 0.f, a2 = 0.f, e0 = 0.f, e1 = 0.f, e2 = 0.f;
-    int b = 0;
-    HOT
-    for (; b + 1 < nbr; b += 2) {
-      const float f0 = bf[b], f1 = bf[b + 1];
-      auto Ja = Jk + b * nv; auto Jb = Jk + (b + 1) * nv;
-      a0 = fmaf(LDJ(Ja[k0]), f0, a0); a1 = fmaf(LDJ(Ja[k1]), f0, a1); a2 = fmaf(LDJ(Ja[k2]), f0, a2);
-      e0 = fmaf(LDJ(Jb[k0]), f1, e0); e1 = fmaf(LDJ(Jb[k1]), f1, e1); e2 = fmaf(LDJ(Jb[k2]), f1, e2);
-    }
-    if (b < nbr) { const float f0 = bf[b]; auto Ja = Jk + b * nv; a0 = fmaf(LDJ(Ja[k0]), f0, a0); a1 = fmaf(LDJ(Ja[k1]), f0, a1); a2 = fmaf(LDJ(Ja[k2]), f0, a2); }
-    out[k0] = res[0] + a0 + e0;
-    if (kb + TEAM < nv) out[kb + TEAM] = res[1] + a1 + e1;
-    if (kb + 2 * TEAM < nv) out[kb + 2 * TEAM] = res[2] + a2 + e2;
-  }
+  if (nv <= 2 * TEAM) jtForce<2>(slot, sm, t, nbr, bf, out); else jtForce<3>(slot, sm, t, nbr, bf, out);
   TSYNC();
 }
 // One point of the 1-D cost along the search direction.  `tol` is the convergence threshold for |d0| at this point:

@@ -40,6 +40,9 @@
 #ifndef MINB_FINISH
 #define MINB_FINISH 2
 #endif
+#ifndef SB
+#define SB 4   // 6: ten blocks = one round of 12 warps, but +2 % step time (registers); 8: +3.5 %
+#endif
 #ifndef SYRK_UNROLL
 #define SYRK_UNROLL 2   // -6 % step time against the compiler's own choice (profiles/r2_ab.txt)
 #endif
@@ -637,13 +640,13 @@ __device__ __noinline__ void hessianAssemble(int slot, SP sm, Tm t, SP H, int nc
       if (nb == 3) {
         HOT
         for (int k = 0; k < nv; k++) {
-          const float jn = LDJ(J[k]), j1 = LDJ(J[nv + k]), j2 = LDJ(J[2 * nv + k]);
+          const float jn = LDJS(J[k]), j1 = LDJS(J[nv + k]), j2 = LDJS(J[2 * nv + k]);
           Uo[k] = fmaf(Wnt1, j2, fmaf(Wnt0, j1, Wnn * jn)); Uo[nv + k] = fmaf(Wnt0, jn, Wtt0 * j1); Uo[2 * nv + k] = fmaf(Wnt1, jn, Wtt1 * j2);
         }
       } else if (nb == 4) {
         HOT
         for (int k = 0; k < nv; k++) {
-          const float jn = LDJ(J[k]), j1 = LDJ(J[nv + k]), j2 = LDJ(J[2 * nv + k]), j3 = LDJ(J[3 * nv + k]);
+          const float jn = LDJS(J[k]), j1 = LDJS(J[nv + k]), j2 = LDJS(J[2 * nv + k]), j3 = LDJS(J[3 * nv + k]);
           Uo[k] = fmaf(Wnt2, j3, fmaf(Wnt1, j2, fmaf(Wnt0, j1, Wnn * jn)));
           Uo[nv + k] = fmaf(Wnt0, jn, Wtt0 * j1); Uo[2 * nv + k] = fmaf(Wnt1, jn, Wtt1 * j2); Uo[3 * nv + k] = fmaf(Wnt2, jn, Wtt2 * j3);
         }
@@ -652,35 +655,35 @@ __device__ __noinline__ void hessianAssemble(int slot, SP sm, Tm t, SP H, int nc
       }
     }
     TSYNC();
-    const int nblk = (nv + 3) >> 2, nB = (nblk * (nblk + 1)) >> 1, nbase = nb * nconT;
+    // SB x SB register blocks of the lower triangle, one per warp at a time; the block's columns are immediate offsets from
+    // two row pointers (clamping them to nv - 1 cost 1.7 % of the step in index arithmetic).  Columns past nv read the next
+    // row / region of the scratch (finite or not, never stored).
+    const int nblk = (nv + SB - 1) / SB, nB = (nblk * (nblk + 1)) >> 1, nbase = nb * nconT;
     for (int blk = t.tl; blk < nB; blk += nw) {
       int R = 0, rem = blk;
       while (rem > R) { rem -= R + 1; R++; }   // blk -> (R, C), C <= R
       const int C = rem;
-      int ri[4], ci[4];
+      float acc[SB][SB];
 #pragma unroll
-      for (int a = 0; a < 4; a++) { ri[a] = min(4 * R + a, nv - 1); ci[a] = min(4 * C + a, nv - 1); }
-      float acc[4][4];
+      for (int a = 0; a < SB; a++)
 #pragma unroll
-      for (int a = 0; a < 4; a++)
-#pragma unroll
-        for (int b = 0; b < 4; b++) acc[a][b] = 0.f;
-      auto Ub = sm + L.conU; auto Jb = sm + L.conJ;
+        for (int b = 0; b < SB; b++) acc[a][b] = 0.f;
+      auto Ub = sm + L.conU + SB * R; auto Jb = sm + L.conJ + SB * C;
       TFOR_PRAGMA(SYRK_UNROLL)
       for (int i = 0; i < nbase; i++) {
-        float u[4], j[4];
+        float u[SB], j[SB];
 #pragma unroll
-        for (int a = 0; a < 4; a++) { u[a] = LDJ(Ub[i * nv + ri[a]]); j[a] = LDJ(Jb[i * nv + ci[a]]); }
+        for (int a = 0; a < SB; a++) { u[a] = LDJ(Ub[i * nv + a]); j[a] = LDJ(Jb[i * nv + a]); }
 #pragma unroll
-        for (int a = 0; a < 4; a++)
+        for (int a = 0; a < SB; a++)
 #pragma unroll
-          for (int b = 0; b < 4; b++) acc[a][b] = fmaf(u[a], j[b], acc[a][b]);
+          for (int b = 0; b < SB; b++) acc[a][b] = fmaf(u[a], j[b], acc[a][b]);
       }
 #pragma unroll
-      for (int a = 0; a < 4; a++)
+      for (int a = 0; a < SB; a++)
 #pragma unroll
-        for (int b = 0; b < 4; b++) {
-          const int r = 4 * R + a, c = 4 * C + b;
+        for (int b = 0; b < SB; b++) {
+          const int r = SB * R + a, c = SB * C + b;
           if (r < nv && c <= r) H[TRI(r) + c] += acc[a][b];
         }
     }
@@ -928,16 +931,17 @@ __device__ __noinline__ int newtonTile(int slot, SP sm, Tm t, const NewtonMem& M
   const float scale = 1.f / (D.meaninertia * (float)max(1, nv));
   // warm start: cheaper of qacc_warmstart and qacc_smooth.  The warm start is evaluated last, so when every world of the
   // tile keeps it (the steady state of a rollout) its row residuals, M qacc and cost are already in place.
-  const float costS = residualCost(slot, sm, t, ncon, nefc, qas);
-  float costW = 3.4e38f, gaussW = 0.f;
+  float costS, costW = 3.4e38f, gaussW = 0.f;
   if (!(D.disableflags & DSBL_WARMSTART)) {
     mulMsparse(slot, sm + L.qM, warm, Ma, t);
     TSYNC();
     float g = 0.f;
     TFOR(k, nv) g = fmaf(0.5f * (Ma[k] - smooth[k]), warm[k] - qas[k], g);
     gaussW = TSUM(g);
-    costW = gaussW + residualCost(slot, sm, t, ncon, nefc, warm);
-  }
+    float c2[2];
+    residualCost2(slot, sm, t, ncon, nefc, qas, warm, c2);   // both candidates in one sweep over J
+    costS = c2[0]; costW = gaussW + c2[1];
+  } else costS = residualCost(slot, sm, t, ncon, nefc, qas);
   const bool useWarm = !(costW > costS);
   TFOR(k, nv) qacc[k] = useWarm ? warm[k] : qas[k];
   TSYNC();
@@ -957,6 +961,7 @@ __device__ __noinline__ int newtonTile(int slot, SP sm, Tm t, const NewtonMem& M
   for (;;) {
     // gradient and termination tests
     constraintForce(slot, sm, t, ncon, nefc, tmp);
+    TICK(15);
     float gg[2] = {0.f, 0.f};
     TFOR(k, nv) {
       const float g = Ma[k] - smooth[k] - tmp[k]; grad[k] = g; search[k] = g; gg[0] = fmaf(g, g, gg[0]);
@@ -983,9 +988,11 @@ __device__ __noinline__ int newtonTile(int slot, SP sm, Tm t, const NewtonMem& M
     if (active && !(sn >= MINVAL)) active = false;
     // exact line search along `search`
     mulMsparse(slot, sm + L.qM, search, Mv, t);
+    TICK(12);
     auto bx = sm + L.basev;
     baseMul(slot, sm, t, ncon, search, bx);
     TSYNC();
+    TICK(13);
     for (int r = t.tl; r < nefc; r += nw) EFC(E_JV, r) = rowMul(slot, sm, r, search, bx);
     float g12[2] = {0.f, 0.f};
     TFOR(k, nv) { g12[0] = fmaf(search[k], Ma[k] - smooth[k], g12[0]); g12[1] = fmaf(0.5f * search[k], Mv[k], g12[1]); }
@@ -1075,7 +1082,8 @@ __device__ __noinline__ int newtonTile(int slot, SP sm, Tm t, const NewtonMem& M
 // manifold; then the state and the per-dof results of the solve go out as full lines.
 // (a device function: the solver kernel runs it as its own tail -- each tile goes on to integrate as soon as ITS solve is
 // done, instead of the whole batch meeting at a kernel boundary first; finishKernel remains for the paths without a solve)
-__device__ __noinline__ void finishTile(int slot, int fslot, SP sm, Tm t, World W, int flags) {
+// `stage`: a shared-memory block of >= nM + 2 nv elements per lane (the solver kernel's, free after the solve), or null
+__device__ __noinline__ void finishTile(int slot, int fslot, SP sm, Tm t, World W, int flags, SP stage) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L; const FieldPtrs& F = tP[slot].F;
   const int nq = D.nq, nv = D.nv, na = D.na, nu = D.nu;
   if (flags & FIN_ACC) {   // results of the solve (read-only here; mj_Euler below does not change them)
@@ -1091,7 +1099,15 @@ __device__ __noinline__ void finishTile(int slot, int fslot, SP sm, Tm t, World 
     const bool skip = __float_as_int(sm[L.wstate + WS_SKIP]) != 0;   // mj_checkAcc reset this world: nothing to integrate
     const float h = D.timestep;
     auto qa = sm + L.tmpv;
-    if (D.any_damping) {
+    if (D.any_damping && stage.p) {
+      // the level-by-level solve is a chain of dependent loads with a barrier per level: run it on a shared-memory copy of
+      // the factor (measured: 5 % of the solver kernel's time when it reads the factor from the scratch)
+      SP LD = stage, dinv = stage + D.nM; qa = dinv + nv;
+      TFOR(e, D.nM) LD[e] = sm[L.qH + e];
+      TFOR(i, nv) { dinv[i] = sm[L.qHinv + i]; qa[i] = sm[L.smooth + i] + sm[L.qfrc_con + i]; }
+      TSYNC();
+      solveLDL(slot, LD, dinv, qa, t);
+    } else if (D.any_damping) {
       TFOR(i, nv) qa[i] = sm[L.smooth + i] + sm[L.qfrc_con + i];
       TSYNC();
       solveLDL(slot, sm + L.qH, sm + L.qHinv, qa, t);
@@ -1146,7 +1162,8 @@ __global__ void __launch_bounds__(32 * MAXW, MINB_FINISH) finishKernel(int slot,
   Timeline tline(slot, MYO_K_FINISH);
   Ctx c = tileCtx(slot, nworld, mask, scratch);
   if (!c.live) return;
-  finishTile(slot, fslot, c.sm, c.t, c.W, flags);
+  SP none; none.p = nullptr;
+  finishTile(slot, fslot, c.sm, c.t, c.W, flags, none);
 }
 
 // mj_makeConstraint as its own launch: it needs the contacts and the velocity, not the smooth forces, so it runs on the
@@ -1228,7 +1245,8 @@ __global__ void __launch_bounds__(32 * MAXW, MINB_NEWTON) newtonKernel(int slot,
   }
   if (fin >= 0) {   // mj_Euler and the state / result outputs of this tile (finishTile)
     TSYNC();
-    finishTile(slot, fslot, sm, t, c.W, fin);
+    SP stage; stage.p = use_smem ? tileShared + lane : nullptr;   // (TRI(nv) + 7 nv elements per lane >= nM + 2 nv)
+    finishTile(slot, fslot, sm, t, c.W, fin, stage);
   }
 }
 

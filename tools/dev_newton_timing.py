@@ -24,8 +24,10 @@ L.myo_debug_timing(d._h, a.ctypes.data_as(ctypes.c_void_p)); a1 = a.reshape(-1, 
 names = ["makeConstraint", "warm start / residuals", "force + gradient", "hessian assemble", "hessian update", "cholesky", "chol solve", "M s, J s", "line search", "update + cost", "final force", "passes"]
 per = a1 / float(B - A)
 print("steps", A, B, "ncon mean %.2f nefc mean %.2f max %d" % (float(d.ncon.float().mean()), float(d.nefc.float().mean()), int(d.nefc.max())))
-tot = per[:, :11].sum(axis=1)
+tot = per[:, :11].sum(axis=1) + per[:, 12:16].sum(axis=1)
 print("tiles", len(per), "cycles per tile per step: mean %.0f  p50 %.0f  max %.0f  (%.1f us at 1.965 GHz max)" % (tot.mean(), np.median(tot), tot.max(), tot.max() / 1965))
 print("passes per tile per step: mean %.2f max %.2f" % (per[:, 11].mean(), per[:, 11].max()))
 for k, nme in enumerate(names[:11]):
     print("%-24s mean %8.0f cycles (%5.1f %%)   per pass %8.0f" % (nme, per[:, k].mean(), 100 * per[:, k].mean() / tot.mean(), per[:, k].mean() / max(per[:, 11].mean(), 1e-9) if k >= 2 and k <= 9 else per[:, k].mean()))
+for k, nme in ((12, "  (M s)"), (13, "  (Jb s + barrier)"), (15, "  (constraintForce)")):
+    print("%-24s mean %8.0f cycles (%5.1f %%)   per pass %8.0f" % (nme, per[:, k].mean(), 100 * per[:, k].mean() / tot.mean(), per[:, k].mean() / max(per[:, 11].mean(), 1e-9)))
