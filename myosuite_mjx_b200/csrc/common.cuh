@@ -171,8 +171,18 @@ struct Tm { int tl, nw; };
 
 // batched field access, struct-of-arrays, world fastest: element k of world w lives at base[k * nworld + w]
 struct World { size_t w, nw; };
-#define OUTF(ptr, k) ((float*)(ptr))[(size_t)(k) * W.nw + W.w]   /* also used to READ input fields */
+// Element k of a [k][nworld] field for this lane's world.  Stores are streaming (st.global.cs, evict-first): the 640 MB of
+// output fields a step writes are never read back by it, and at plain priority they push the solver's working set (the
+// tiles' Jacobian blocks, ~100 MB at 8192 worlds, about the size of the L2) out to DRAM.  Reads (input fields) are plain.
+#ifndef NO_STREAM_OUT
+struct FRef { float* p; __device__ __forceinline__ void operator=(float v) const { __stcs(p, v); } __device__ __forceinline__ operator float() const { return *p; } };
+struct IRef { int* p; __device__ __forceinline__ void operator=(int v) const { __stcs(p, v); } __device__ __forceinline__ operator int() const { return *p; } };
+#define OUTF(ptr, k) (FRef{(float*)(ptr) + ((size_t)(k) * W.nw + W.w)})
+#define OUTI(ptr, k) (IRef{(int*)(ptr) + ((size_t)(k) * W.nw + W.w)})
+#else
+#define OUTF(ptr, k) ((float*)(ptr))[(size_t)(k) * W.nw + W.w]
 #define OUTI(ptr, k) ((int*)(ptr))[(size_t)(k) * W.nw + W.w]
+#endif
 // ------------------------------------------------------------------------------------------ kinematics
 __device__ __noinline__ void kinematics(int slot, SP sm, Tm t) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
