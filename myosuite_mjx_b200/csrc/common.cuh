@@ -1411,6 +1411,35 @@ __device__ __forceinline__ float rowMul(int slot, SP sm, int r, SP x, SP bx) {
   return coef * acc;
 }
 
+// Row loops of the solver: a warp owns rows r = tl, tl + nw, ... and is bound by the latency of their loads (scratch, mostly
+// L1 misses), so the loops take RB rows per iteration and issue all their loads before the first use.  (The compiler cannot
+// do it: it cannot prove that the store to one row's record does not alias the next row's loads.)  Sums keep the row order.
+#ifndef RB
+#define RB 4
+#endif
+// J_r . x for RB rows (r0, r0 + nw, ...); contact rows -- the common case -- with their base products loaded together
+__device__ __forceinline__ void rowMulBatch(int slot, SP sm, int r0, int nw, int nefc, SP x, SP bx, float* out) {
+  const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
+  int d0[RB], q1[RB]; float cf[RB];
+#pragma unroll
+  for (int u = 0; u < RB; u++) {
+    const int r = r0 + u * nw; const bool ok = r < nefc;
+    d0[u] = ok ? EFCI(E_DESC0, r) : ROW_CON; cf[u] = ok ? EFC(E_COEF, r) : 0.f; q1[u] = ok ? EFCI(E_DESC1, r) : -1;
+  }
+  float ba[RB], bb[RB];
+#pragma unroll
+  for (int u = 0; u < RB; u++) {
+    const bool con = (d0[u] & 3) == ROW_CON;
+    ba[u] = bx[con ? d0[u] >> 2 : 0]; bb[u] = bx[con && q1[u] >= 0 ? q1[u] : 0];
+  }
+#pragma unroll
+  for (int u = 0; u < RB; u++) {
+    const int r = r0 + u * nw;
+    if ((d0[u] & 3) == ROW_CON) out[u] = ba[u] + (q1[u] >= 0 ? cf[u] * bb[u] : 0.f);
+    else out[u] = r < nefc ? rowMul(slot, sm, r, x, bx) : 0.f;
+  }
+}
+
 // ------------------------------------------------------------------------------------------ Newton solver (mj_fwdConstraint)
 __device__ __noinline__ void mulMsparse(int slot, SP qM, SP x, SP out, Tm t) {
   const DevModel& D = tP[slot].D;
@@ -1448,13 +1477,25 @@ __device__ __noinline__ void residualCost2(int slot, SP sm, Tm t, int ncon, int 
   baseMul2(slot, sm, t, ncon, x0, x1, bx0, bx1);
   TSYNC();
   float c[2] = {0.f, 0.f};
-  TFOR(r, nefc) {
-    const float aref = EFC(E_AREF, r), Dr = EFC(E_D, r);
-    const int d0 = EFCI(E_DESC0, r);
-    const float jar0 = rowMul(slot, sm, r, x0, bx0) - aref, jar1 = rowMul(slot, sm, r, x1, bx1) - aref;
-    EFC(E_JAR, r) = jar1;
-    if (rowOn(d0, jar0)) c[0] = fmaf(0.5f * Dr * jar0, jar0, c[0]);
-    if (rowOn(d0, jar1)) c[1] = fmaf(0.5f * Dr * jar1, jar1, c[1]);
+  for (int rb = t.tl; rb < nefc; rb += RB * TEAM) {
+    float aref[RB], Dr[RB], j0[RB], j1[RB]; int d0[RB];
+#pragma unroll
+    for (int u = 0; u < RB; u++) {
+      const int r = rb + u * TEAM; const bool ok = r < nefc;
+      aref[u] = ok ? EFC(E_AREF, r) : 0.f; Dr[u] = ok ? EFC(E_D, r) : 0.f; d0[u] = ok ? EFCI(E_DESC0, r) : ROW_CON;
+    }
+    rowMulBatch(slot, sm, rb, TEAM, nefc, x0, bx0, j0);
+    rowMulBatch(slot, sm, rb, TEAM, nefc, x1, bx1, j1);
+#pragma unroll
+    for (int u = 0; u < RB; u++) {
+      const int r = rb + u * TEAM;
+      if (r < nefc) {
+        const float jar0 = j0[u] - aref[u], jar1 = j1[u] - aref[u];
+        EFC(E_JAR, r) = jar1;
+        if (rowOn(d0[u], jar0)) c[0] = fmaf(0.5f * Dr[u] * jar0, jar0, c[0]);
+        if (rowOn(d0[u], jar1)) c[1] = fmaf(0.5f * Dr[u] * jar1, jar1, c[1]);
+      }
+    }
   }
   TSYNC();
   cost[0] = TSUM(c[0]); cost[1] = TSUM(c[1]);
@@ -1521,8 +1562,24 @@ template <int G> __device__ __forceinline__ void jtForce(int slot, SP sm, Tm t, 
 __device__ __noinline__ void constraintForce(int slot, SP sm, Tm t, int ncon, int nefc, SP out) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
   const int nv = D.nv, nb = D.maxbase;
-  TFOR(r, nefc) { const float jar = EFC(E_JAR, r); EFC(E_FORCE, r) = rowOn(EFCI(E_DESC0, r), jar) ? -EFC(E_D, r) * jar : 0.f; }
+#ifdef CF_TICKS
+  long long* dbg = tP[slot].X.dbg; long long tlast = dbg ? clock64() : 0;
+#define CFT(k) do { if (dbg && threadIdx.x == 0) { const long long now_ = clock64(); dbg[blockIdx.x * 32 + (k)] += now_ - tlast; tlast = now_; } } while (0)
+#else
+#define CFT(k)
+#endif
+  for (int rb = t.tl; rb < nefc; rb += RB * TEAM) {
+    float jar[RB], Dr[RB]; int d0[RB];
+#pragma unroll
+    for (int u = 0; u < RB; u++) {
+      const int r = rb + u * TEAM; const bool ok = r < nefc;
+      jar[u] = ok ? EFC(E_JAR, r) : 0.f; Dr[u] = ok ? EFC(E_D, r) : 0.f; d0[u] = ok ? EFCI(E_DESC0, r) : ROW_CON;
+    }
+#pragma unroll
+    for (int u = 0; u < RB; u++) { const int r = rb + u * TEAM; if (r < nefc) EFC(E_FORCE, r) = rowOn(d0[u], jar[u]) ? -Dr[u] * jar[u] : 0.f; }
+  }
   TSYNC();
+  CFT(16);
   auto bf = sm + L.basev + nb * D.nconmax;
   TFOR(c, ncon) {   // base-row forces of one contact from its pyramid rows (mju_decodePyramid, transposed)
     auto cr = sm + L.con + 12 * c;
@@ -1539,9 +1596,11 @@ __device__ __noinline__ void constraintForce(int slot, SP sm, Tm t, int ncon, in
     for (int k = 0; k < nb; k++) bf[c * nb + k] = fb[k];
   }
   TSYNC();
+  CFT(17);
   const int nbr = nb * ncon;
   if (nv <= 2 * TEAM) jtForce<2>(slot, sm, t, nbr, bf, out); else jtForce<3>(slot, sm, t, nbr, bf, out);
   TSYNC();
+  CFT(18);
 }
 // One point of the 1-D cost along the search direction.  `tol` is the convergence threshold for |d0| at this point:
 // MuJoCo's gtol, or the float32 noise floor of the derivative sum when that is larger (the sum cancels to ~eps * mag

@@ -40,11 +40,9 @@
 #ifndef MINB_FINISH
 #define MINB_FINISH 2
 #endif
-#ifndef SB
-#define SB 4   // 6: ten blocks = one round of 12 warps, but +2 % step time (registers); 8: +3.5 %
-#endif
+// (syrk block size: 6 x 6 = ten blocks, one round of 12 warps, was +2 % step time (registers); 8 x 8 +3.5 %)
 #ifndef SYRK_UNROLL
-#define SYRK_UNROLL 2   // -6 % step time against the compiler's own choice (profiles/r2_ab.txt)
+#define SYRK_UNROLL 1   // (contacts per iteration of the syrk: 24 J loads each; 2: +0.5 % step time)
 #endif
 namespace {
 
@@ -567,6 +565,59 @@ __device__ __noinline__ int makeConstraintTile(int slot, SP sm, Tm t, int ncon, 
   return nefc;
 }
 
+// H += Jb^T (W Jb) over the tile's contacts, in 4 x 4 register blocks of the lower triangle, one block per warp at a time.
+// The weighted rows U = W Jb (W: the contact's symmetric weight matrix in base-row space, conW) are formed in registers from
+// the NB base rows of each contact -- as many loads as reading a stored U, no U sweep, and half the Jacobian footprint in L2.
+// The block's columns are immediate offsets from two row pointers (clamping them to nv - 1 cost 1.7 % of the step in index
+// arithmetic); columns past nv read the next row / region of the scratch (finite or not, never stored).
+template <int NB> __device__ __forceinline__ void syrkBlocks(int slot, SP sm, Tm t, SP H, int nconT) {
+  const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
+  const int nv = D.nv, nw = t.nw;
+  const int nblk = (nv + 3) >> 2, nB = (nblk * (nblk + 1)) >> 1;
+  for (int blk = t.tl; blk < nB; blk += nw) {
+    int R = 0, rem = blk;
+    while (rem > R) { rem -= R + 1; R++; }   // blk -> (R, C), C <= R
+    const int C = rem;
+    float acc[4][4];
+#pragma unroll
+    for (int a = 0; a < 4; a++)
+#pragma unroll
+      for (int b = 0; b < 4; b++) acc[a][b] = 0.f;
+    auto Jr = sm + L.conJ + 4 * R; auto Jc = sm + L.conJ + 4 * C;
+    TFOR_PRAGMA(SYRK_UNROLL)
+    for (int c = 0; c < nconT; c++) {
+      auto Wi = sm + L.conW + 8 * c;
+      float jr[NB][4], jc[NB][4], Wn[NB], Wt[NB];
+#pragma unroll
+      for (int b = 0; b < NB; b++) {
+        Wn[b] = Wi[b]; Wt[b] = b > 0 ? Wi[3 + b] : 0.f;   // Wn = (Wnn, Wnt[0..]), Wt = (-, Wtt[0..])
+#pragma unroll
+        for (int a = 0; a < 4; a++) { jr[b][a] = LDJ(Jr[(c * NB + b) * nv + a]); jc[b][a] = LDJ(Jc[(c * NB + b) * nv + a]); }
+      }
+#pragma unroll
+      for (int a = 0; a < 4; a++) {
+        float u = Wn[0] * jr[0][a];   // U row of the normal: Wnn jn + sum_q Wnt[q] jq
+#pragma unroll
+        for (int b = 1; b < NB; b++) u = fmaf(Wn[b], jr[b][a], u);
+#pragma unroll
+        for (int q = 0; q < 4; q++) acc[a][q] = fmaf(u, jc[0][q], acc[a][q]);
+#pragma unroll
+        for (int b = 1; b < NB; b++) {
+          const float ub = fmaf(Wn[b], jr[0][a], Wt[b] * jr[b][a]);   // U row of tangent b: Wnt jn + Wtt jb
+#pragma unroll
+          for (int q = 0; q < 4; q++) acc[a][q] = fmaf(ub, jc[b][q], acc[a][q]);
+        }
+      }
+    }
+#pragma unroll
+    for (int a = 0; a < 4; a++)
+#pragma unroll
+      for (int b = 0; b < 4; b++) {
+        const int r = 4 * R + a, c = 4 * C + b;
+        if (r < nv && c <= r) H[TRI(r) + c] += acc[a][b];
+      }
+  }
+}
 // H = M + J^T D_active J (lower triangle, row-packed) and its Cholesky factor; Hd receives the factor's diagonal.
 // Contacts enter through their base rows (normal, tangents, torsion): with W the small symmetric weight matrix of a
 // contact's active pyramid rows in base-row space, J^T D J = Jb^T (W Jb) =: Jb^T U, a dense [nv x nbase] x [nbase x nv]
@@ -632,61 +683,9 @@ __device__ __noinline__ void hessianAssemble(int slot, SP sm, Tm t, SP H, int nc
       Wo[0] = Wnn; Wo[1] = Wnt[0]; Wo[2] = Wnt[1]; Wo[3] = Wnt[2]; Wo[4] = Wtt[0]; Wo[5] = Wtt[1]; Wo[6] = Wtt[2];
     }
     TSYNC();
-    // U = W Jb: a warp takes whole contacts and walks their dofs
-    for (int c = t.tl; c < nconT; c += nw) {
-      auto Wi = sm + L.conW + 8 * c;
-      const float Wnn = Wi[0], Wnt0 = Wi[1], Wnt1 = Wi[2], Wnt2 = Wi[3], Wtt0 = Wi[4], Wtt1 = Wi[5], Wtt2 = Wi[6];
-      auto J = sm + L.conJ + (c * nb) * nv; auto Uo = sm + L.conU + (c * nb) * nv;
-      if (nb == 3) {
-        HOT
-        for (int k = 0; k < nv; k++) {
-          const float jn = LDJS(J[k]), j1 = LDJS(J[nv + k]), j2 = LDJS(J[2 * nv + k]);
-          Uo[k] = fmaf(Wnt1, j2, fmaf(Wnt0, j1, Wnn * jn)); Uo[nv + k] = fmaf(Wnt0, jn, Wtt0 * j1); Uo[2 * nv + k] = fmaf(Wnt1, jn, Wtt1 * j2);
-        }
-      } else if (nb == 4) {
-        HOT
-        for (int k = 0; k < nv; k++) {
-          const float jn = LDJS(J[k]), j1 = LDJS(J[nv + k]), j2 = LDJS(J[2 * nv + k]), j3 = LDJS(J[3 * nv + k]);
-          Uo[k] = fmaf(Wnt2, j3, fmaf(Wnt1, j2, fmaf(Wnt0, j1, Wnn * jn)));
-          Uo[nv + k] = fmaf(Wnt0, jn, Wtt0 * j1); Uo[2 * nv + k] = fmaf(Wnt1, jn, Wtt1 * j2); Uo[3 * nv + k] = fmaf(Wnt2, jn, Wtt2 * j3);
-        }
-      } else {
-        for (int k = 0; k < nv; k++) Uo[k] = Wnn * J[k];
-      }
-    }
-    TSYNC();
-    // SB x SB register blocks of the lower triangle, one per warp at a time; the block's columns are immediate offsets from
-    // two row pointers (clamping them to nv - 1 cost 1.7 % of the step in index arithmetic).  Columns past nv read the next
-    // row / region of the scratch (finite or not, never stored).
-    const int nblk = (nv + SB - 1) / SB, nB = (nblk * (nblk + 1)) >> 1, nbase = nb * nconT;
-    for (int blk = t.tl; blk < nB; blk += nw) {
-      int R = 0, rem = blk;
-      while (rem > R) { rem -= R + 1; R++; }   // blk -> (R, C), C <= R
-      const int C = rem;
-      float acc[SB][SB];
-#pragma unroll
-      for (int a = 0; a < SB; a++)
-#pragma unroll
-        for (int b = 0; b < SB; b++) acc[a][b] = 0.f;
-      auto Ub = sm + L.conU + SB * R; auto Jb = sm + L.conJ + SB * C;
-      TFOR_PRAGMA(SYRK_UNROLL)
-      for (int i = 0; i < nbase; i++) {
-        float u[SB], j[SB];
-#pragma unroll
-        for (int a = 0; a < SB; a++) { u[a] = LDJ(Ub[i * nv + a]); j[a] = LDJ(Jb[i * nv + a]); }
-#pragma unroll
-        for (int a = 0; a < SB; a++)
-#pragma unroll
-          for (int b = 0; b < SB; b++) acc[a][b] = fmaf(u[a], j[b], acc[a][b]);
-      }
-#pragma unroll
-      for (int a = 0; a < SB; a++)
-#pragma unroll
-        for (int b = 0; b < SB; b++) {
-          const int r = SB * R + a, c = SB * C + b;
-          if (r < nv && c <= r) H[TRI(r) + c] += acc[a][b];
-        }
-    }
+    if (nb == 3) syrkBlocks<3>(slot, sm, t, H, nconT);
+    else if (nb == 4) syrkBlocks<4>(slot, sm, t, H, nconT);
+    else syrkBlocks<1>(slot, sm, t, H, nconT);
     TSYNC();
   }
   TFOR(i, TRI(nv)) sm[L.Hsave + i] = H[i];   // keep the unfactored matrix: later passes of the tile update it (hessianUpdate)
@@ -694,10 +693,16 @@ __device__ __noinline__ void hessianAssemble(int slot, SP sm, Tm t, SP H, int nc
 // Later Newton passes of a tile: only the rows whose active state flipped in the last line search change H, each by a
 // sparse rank-1 term +-D_r J_r^T J_r (the flags were left in E_JV by the row update).  One warp applies them, every lane
 // walking its own flipped rows -- a few hundred instructions against the dense rebuild's ~10^5.
-__device__ __noinline__ void hessianUpdate(int slot, SP sm, Tm t, SP H, int nefc) {
+__device__ __noinline__ void hessianUpdate(int slot, SP sm, Tm t, SP H, int nefc, SP va, SP vb) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
-  const int nv = D.nv, nb = D.maxbase, nw = t.nw;
-  TFOR(i, TRI(nv)) H[i] = sm[L.Hsave + i];
+  const int nv = D.nv, nw = t.nw;
+  for (int i0 = t.tl; i0 < TRI(nv); i0 += 8 * nw) {   // (eight loads in flight: a plain striped loop pays one scratch latency per element)
+    float h[8];
+#pragma unroll
+    for (int u = 0; u < 8; u++) h[u] = i0 + u * nw < TRI(nv) ? sm[L.Hsave + i0 + u * nw] : 0.f;
+#pragma unroll
+    for (int u = 0; u < 8; u++) if (i0 + u * nw < TRI(nv)) H[i0 + u * nw] = h[u];
+  }
   // Each lane's flipped rows as a list (E_FORCE is free between the force evaluations): the lanes of a warp then take their
   // i-th flipped row together -- walking all rows instead would run the update body once per row that flipped in ANY of the
   // 32 worlds, with one or two lanes active each time.
@@ -711,51 +716,47 @@ __device__ __noinline__ void hessianUpdate(int slot, SP sm, Tm t, SP H, int nefc
   for (int r = r0; r < r1; r++) if (EFC(E_JV, r) != 0.f) { EFC(E_FORCE, at) = __int_as_float(r); at++; }
   const int nflip = sc.total;
   TSYNC();
-  // every warp walks the lane's list but applies only the H rows it owns (a % nw == its index): no two warps touch one entry
-  for (int i = 0; i < nflip; i++) {
-    const int r = EFCI(E_FORCE, i);
-    const float s = EFC(E_JV, r) * EFC(E_D, r);
-    const int d0 = EFCI(E_DESC0, r), type = d0 & 3, id = d0 >> 2;
-    const float coef = EFC(E_COEF, r);
-    if (type == ROW_LIMJ) { const int k = D.limj_dof[id]; if (k % nw == t.tl) H[TRI(k) + k] += s; }
-    else if (type == ROW_CON) {
-      const int bt = EFCI(E_DESC1, r), c = id / nb;
-      auto cr = sm + L.con + 12 * c;
-      const unsigned mlo = (unsigned)__float_as_int(cr[10]), mhi = (unsigned)__float_as_int(cr[11]);
-      auto Jn = sm + L.conJ + id * nv; auto Jt = sm + L.conJ + (bt >= 0 ? bt : id) * nv;
-      const float ct = bt >= 0 ? coef : 0.f;
-      for (int half = 0; half < 2; half++) {
-        unsigned wa = half ? mhi : mlo;
-        while (wa) {
-          const int a = 32 * half + __ffs((int)wa) - 1;
-          wa &= wa - 1u;
-          if (a % nw != t.tl) continue;
-          const float ja = s * fmaf(ct, Jt[a], Jn[a]);
-          auto Ha = H + TRI(a);
-          for (int h2 = 0; h2 <= half; h2++) {
-            unsigned wb = h2 ? mhi : mlo;
-            if (h2 == half) wb &= (2u << (a & 31)) - 1u;   // columns up to the diagonal
-            while (wb) {
-              const int b = 32 * h2 + __ffs((int)wb) - 1;
-              wb &= wb - 1u;
-              Ha[b] = fmaf(ja, fmaf(ct, Jt[b], Jn[b]), Ha[b]);
-            }
-          }
-        }
-      }
-    } else if (type == ROW_LIMT) {
-      const int tn = D.limt_ten[id], n0 = D.ten_nzstart[tn], n1 = D.ten_nzstart[tn + 1];
-      for (int a = n0; a < n1; a++) {
-        const int da = D.nz_dof[a];
-        if (da % nw != t.tl) continue;
-        for (int b = n0; b < n1; b++) {
-          const int db = D.nz_dof[b];
-          if (da >= db) H[TRI(da) + db] += s * sm[L.tenJ + a] * sm[L.tenJ + b];   // coef^2 = 1
-        }
+  // Two flipped rows per round: the tile's warps expand them into dense vectors v (nv entries per lane, shared memory; one
+  // round of coalesced J loads), then add s v v^T to the rows of H they own (rows a and nv - 1 - a: equal work per warp).
+  // A lane whose list is shorter rides along with s = 0.  (Walking the rows' dof bit sets per warp instead put ~10
+  // dependent pairs of J loads on every warp's chain for each flip: 52 K cycles per update against 97 K for a full assembly.)
+  const int nflipT = __reduce_max_sync(__activemask(), nflip);
+  SP v[2] = {va, vb};
+  for (int i0 = 0; i0 < nflipT; i0 += 2) {
+    float sc2[2];
+#pragma unroll
+    for (int q = 0; q < 2; q++) {
+      const bool on = i0 + q < nflip;
+      const int r = on ? EFCI(E_FORCE, i0 + q) : 0;
+      sc2[q] = on ? EFC(E_JV, r) * EFC(E_D, r) : 0.f;
+      const int d0 = on ? EFCI(E_DESC0, r) : ROW_LIMJ, type = d0 & 3, id = d0 >> 2;
+      if (type == ROW_CON) {
+        const int bt = EFCI(E_DESC1, r);
+        const float ct = bt >= 0 ? EFC(E_COEF, r) : 0.f;
+        auto Jn = sm + L.conJ + id * nv; auto Jt = sm + L.conJ + (bt >= 0 ? bt : id) * nv;
+        TFOR(k, nv) v[q][k] = fmaf(ct, Jt[k], Jn[k]);
+      } else if (type == ROW_LIMJ) {
+        const int kd = on ? D.limj_dof[id] : -1;
+        TFOR(k, nv) v[q][k] = k == kd ? 1.f : 0.f;
+      } else {   // tendon limit: the tendon's sparse row (coef^2 = 1)
+        const int tn = D.limt_ten[id], n0 = D.ten_nzstart[tn], n1 = D.ten_nzstart[tn + 1];
+        TFOR(k, nv) { float a = 0.f; for (int n = n0; n < n1; n++) if (D.nz_dof[n] == k) a += sm[L.tenJ + n]; v[q][k] = a; }
       }
     }
+    TSYNC();
+    for (int a0 = t.tl; a0 < (nv + 1) / 2; a0 += nw) {
+#pragma unroll
+      for (int h = 0; h < 2; h++) {
+        const int a = h ? nv - 1 - a0 : a0;
+        if (h && a == a0) break;
+        const float wa = sc2[0] * v[0][a], wb = sc2[1] * v[1][a];
+        auto Ha = H + TRI(a);
+        HOT
+        for (int b = 0; b <= a; b++) Ha[b] = fmaf(wb, v[1][b], fmaf(wa, v[0][b], Ha[b]));
+      }
+    }
+    TSYNC();
   }
-  TSYNC();
   TFOR(i, TRI(nv)) sm[L.Hsave + i] = H[i];
 }
 // Blocked left-looking Cholesky of H in place (L L^T = H), panels of CHB columns, two barriers per panel: (1) every row at
@@ -894,16 +895,27 @@ template <int K> __device__ __forceinline__ void lsEvalTile(int slot, SP sm, Tm 
 #pragma unroll
   for (int i = 0; i < 4 * K; i++) q[i] = 0.f;
   const int neq = D.neq;
-  TFOR_PRAGMA(2)
-  for (int r = t.tl; r < nefc; r += t.nw) {
-    const float jar = EFC(E_JAR, r), jv = EFC(E_JV, r), Dr = EFC(E_D, r);
+  for (int rb = t.tl; rb < nefc; rb += RB * t.nw) {
+    float jarv[RB], jvv[RB], Drv[RB];
 #pragma unroll
-    for (int k = 0; k < K; k++) {
-      const float x = fmaf(a[k], jv, jar);
-      if (r < neq || x < 0.f) {   // equality rows come first and are always active
-        const float dj = Dr * jar;
-        q[4 * k] = fmaf(0.5f * dj, jar, q[4 * k]); q[4 * k + 1] = fmaf(dj, jv, q[4 * k + 1]);
-        q[4 * k + 2] = fmaf(0.5f * Dr * jv, jv, q[4 * k + 2]); q[4 * k + 3] = fmaf(fabsf(dj), fabsf(jv), q[4 * k + 3]);
+    for (int u = 0; u < RB; u++) {
+      const int r = rb + u * t.nw; const bool ok = r < nefc;
+      jarv[u] = ok ? EFC(E_JAR, r) : 0.f; jvv[u] = ok ? EFC(E_JV, r) : 0.f; Drv[u] = ok ? EFC(E_D, r) : 0.f;
+    }
+#pragma unroll
+    for (int u = 0; u < RB; u++) {
+      const int r = rb + u * t.nw;
+      const float jar = jarv[u], jv = jvv[u], Dr = Drv[u];
+      if (r < nefc) {
+#pragma unroll
+        for (int k = 0; k < K; k++) {
+          const float x = fmaf(a[k], jv, jar);
+          if (r < neq || x < 0.f) {   // equality rows come first and are always active
+            const float dj = Dr * jar;
+            q[4 * k] = fmaf(0.5f * dj, jar, q[4 * k]); q[4 * k + 1] = fmaf(dj, jv, q[4 * k + 1]);
+            q[4 * k + 2] = fmaf(0.5f * Dr * jv, jv, q[4 * k + 2]); q[4 * k + 3] = fmaf(fabsf(dj), fabsf(jv), q[4 * k + 3]);
+          }
+        }
       }
     }
   }
@@ -975,7 +987,7 @@ __device__ __noinline__ int newtonTile(int slot, SP sm, Tm t, const NewtonMem& M
     if (active && iter >= D.iterations) { *status |= MYO_WORLD_SOLVER_MAXITER; active = false; }
     TICK(2);
     if (!__ballot_sync(lmask, active)) break;   // the tile is done when its slowest world is
-    if (pass == 0) { hessianAssemble(slot, sm, t, M.H, ncon, nconT, nefc); TICK(3); } else { hessianUpdate(slot, sm, t, M.H, nefc); TICK(4); }
+    if (pass == 0) { hessianAssemble(slot, sm, t, M.H, ncon, nconT, nefc); TICK(3); } else { hessianUpdate(slot, sm, t, M.H, nefc, M.grad, M.Mv); TICK(4); }   // (grad, Mv: free between the gradient and the solve)
     choleskyTile(nv, M.H, M.Hd, t);
     TICK(5);
     pass++;
@@ -993,7 +1005,12 @@ __device__ __noinline__ int newtonTile(int slot, SP sm, Tm t, const NewtonMem& M
     baseMul(slot, sm, t, ncon, search, bx);
     TSYNC();
     TICK(13);
-    for (int r = t.tl; r < nefc; r += nw) EFC(E_JV, r) = rowMul(slot, sm, r, search, bx);
+    for (int rb = t.tl; rb < nefc; rb += RB * nw) {
+      float jv[RB];
+      rowMulBatch(slot, sm, rb, nw, nefc, search, bx, jv);
+#pragma unroll
+      for (int u = 0; u < RB; u++) if (rb + u * nw < nefc) EFC(E_JV, rb + u * nw) = jv[u];
+    }
     float g12[2] = {0.f, 0.f};
     TFOR(k, nv) { g12[0] = fmaf(search[k], Ma[k] - smooth[k], g12[0]); g12[1] = fmaf(0.5f * search[k], Mv[k], g12[1]); }
     tileSumN<2>(t, g12);   // its barriers also publish E_JV
@@ -1047,15 +1064,27 @@ __device__ __noinline__ int newtonTile(int slot, SP sm, Tm t, const NewtonMem& M
     if (active && alpha == 0.f) active = false;
     if (active) TFOR(k, nv) { qacc[k] = fmaf(alpha, search[k], qacc[k]); Ma[k] = fmaf(alpha, Mv[k], Ma[k]); }
     float gc[2] = {0.f, 0.f};
-    for (int r = t.tl; r < nefc; r += nw) {
-      float jar = EFC(E_JAR, r), flip = 0.f;
-      if (active) {
-        const float old = jar;
-        jar = fmaf(alpha, EFC(E_JV, r), jar); EFC(E_JAR, r) = jar;
-        flip = (jar < 0.f ? 1.f : 0.f) - (old < 0.f ? 1.f : 0.f);   // the row joins (+1) or leaves (-1) the active set: hessianUpdate
+    for (int rb = t.tl; rb < nefc; rb += RB * nw) {
+      float jarv[RB], jvv[RB], Drv[RB]; int d0v[RB];
+#pragma unroll
+      for (int u = 0; u < RB; u++) {
+        const int r = rb + u * nw; const bool ok = r < nefc;
+        jarv[u] = ok ? EFC(E_JAR, r) : 0.f; jvv[u] = ok ? EFC(E_JV, r) : 0.f; Drv[u] = ok ? EFC(E_D, r) : 0.f; d0v[u] = ok ? EFCI(E_DESC0, r) : ROW_CON;
       }
-      EFC(E_JV, r) = flip;
-      if (rowOn(EFCI(E_DESC0, r), jar)) gc[1] = fmaf(0.5f * EFC(E_D, r) * jar, jar, gc[1]);
+#pragma unroll
+      for (int u = 0; u < RB; u++) {
+        const int r = rb + u * nw;
+        if (r < nefc) {
+          float jar = jarv[u], flip = 0.f;
+          if (active) {
+            const float old = jar;
+            jar = fmaf(alpha, jvv[u], jar); EFC(E_JAR, r) = jar;
+            flip = (jar < 0.f ? 1.f : 0.f) - (old < 0.f ? 1.f : 0.f);   // the row joins (+1) or leaves (-1) the active set: hessianUpdate
+          }
+          EFC(E_JV, r) = flip;
+          if (rowOn(d0v[u], jar)) gc[1] = fmaf(0.5f * Drv[u] * jar, jar, gc[1]);
+        }
+      }
     }
     TSYNC();
     TFOR(k, nv) gc[0] = fmaf(0.5f * (Ma[k] - smooth[k]), qacc[k] - qas[k], gc[0]);

@@ -29,5 +29,5 @@ print("tiles", len(per), "cycles per tile per step: mean %.0f  p50 %.0f  max %.0
 print("passes per tile per step: mean %.2f max %.2f" % (per[:, 11].mean(), per[:, 11].max()))
 for k, nme in enumerate(names[:11]):
     print("%-24s mean %8.0f cycles (%5.1f %%)   per pass %8.0f" % (nme, per[:, k].mean(), 100 * per[:, k].mean() / tot.mean(), per[:, k].mean() / max(per[:, 11].mean(), 1e-9) if k >= 2 and k <= 9 else per[:, k].mean()))
-for k, nme in ((12, "  (M s)"), (13, "  (Jb s + barrier)"), (15, "  (constraintForce)")):
+for k, nme in ((12, "  (M s)"), (13, "  (Jb s + barrier)"), (15, "  (constraintForce)"), (16, "    (cf: row forces)"), (17, "    (cf: base forces)"), (18, "    (cf: J^T f)")):
     print("%-24s mean %8.0f cycles (%5.1f %%)   per pass %8.0f" % (nme, per[:, k].mean(), 100 * per[:, k].mean() / tot.mean(), per[:, k].mean() / max(per[:, 11].mean(), 1e-9)))
