@@ -1446,10 +1446,22 @@ __device__ __noinline__ void mulMsparse(int slot, SP qM, SP x, SP out, Tm t) {
   TFOR(i, D.nv) {
     const int a = D.dof_Madr[i], d = D.dof_rowlen[i];
     float acc = 0.f;
-    HOT
-    for (int q = 0; q < d; q++) acc = fmaf(qM[a + q], x[D.M_col[a + q]], acc);
-    HOT
-    for (int e = D.desc_start[i]; e < D.desc_start[i + 1]; e++) acc = fmaf(qM[D.desc_idx[e]], x[D.desc_dof[e]], acc);
+    // (eight entries of M loaded together: one scratch latency per row part instead of one per entry; same summation order)
+    for (int q0 = 0; q0 < d; q0 += 8) {
+      float m[8];
+#pragma unroll
+      for (int u = 0; u < 8; u++) m[u] = q0 + u < d ? qM[a + q0 + u] : 0.f;
+#pragma unroll
+      for (int u = 0; u < 8; u++) if (q0 + u < d) acc = fmaf(m[u], x[D.M_col[a + q0 + u]], acc);
+    }
+    const int e1 = D.desc_start[i + 1];
+    for (int e0 = D.desc_start[i]; e0 < e1; e0 += 8) {
+      float m[8];
+#pragma unroll
+      for (int u = 0; u < 8; u++) m[u] = e0 + u < e1 ? qM[D.desc_idx[e0 + u]] : 0.f;
+#pragma unroll
+      for (int u = 0; u < 8; u++) if (e0 + u < e1) acc = fmaf(m[u], x[D.desc_dof[e0 + u]], acc);
+    }
     out[i] = acc;
   }
 }
@@ -1581,19 +1593,39 @@ __device__ __noinline__ void constraintForce(int slot, SP sm, Tm t, int ncon, in
   TSYNC();
   CFT(16);
   auto bf = sm + L.basev + nb * D.nconmax;
-  TFOR(c, ncon) {   // base-row forces of one contact from its pyramid rows (mju_decodePyramid, transposed)
-    auto cr = sm + L.con + 12 * c;
-    const int adr = __float_as_int(cr[8]), dim = __float_as_int(cr[9]);
-    float fb[4] = {0.f, 0.f, 0.f, 0.f};
-    if (adr >= 0) {
-      if (dim == 1) fb[0] = EFC(E_FORCE, adr);
-      else
-        for (int k = 1; k < dim; k++) {
-          const float fp = EFC(E_FORCE, adr + 2 * (k - 1)), fm = EFC(E_FORCE, adr + 2 * (k - 1) + 1);
-          fb[0] += fp + fm; fb[k] = EFC(E_COEF, adr + 2 * (k - 1)) * (fp - fm);
-        }
+  // base-row forces of a contact from its pyramid rows (mju_decodePyramid, transposed); two contacts per iteration, their
+  // record loads and then their row loads issued together
+  for (int cb = t.tl; cb < ncon; cb += 2 * TEAM) {
+    int adr[2], dim[2];
+#pragma unroll
+    for (int u = 0; u < 2; u++) {
+      const int c = cb + u * TEAM; const bool ok = c < ncon;
+      auto cr = sm + L.con + 12 * (ok ? c : cb);
+      adr[u] = ok ? __float_as_int(cr[8]) : -1; dim[u] = __float_as_int(cr[9]);
     }
-    for (int k = 0; k < nb; k++) bf[c * nb + k] = fb[k];
+    float fr[2][6], mu[2][3];   // rows of a contact: 2 (dim - 1) <= 6, friction coefficients of its tangent pairs
+#pragma unroll
+    for (int u = 0; u < 2; u++) {
+      const int n = adr[u] < 0 ? 0 : (dim[u] == 1 ? 1 : 2 * (dim[u] - 1));
+#pragma unroll
+      for (int k = 0; k < 6; k++) fr[u][k] = k < n ? EFC(E_FORCE, adr[u] + k) : 0.f;
+#pragma unroll
+      for (int k = 0; k < 3; k++) mu[u][k] = (dim[u] > 1 && 2 * k < n) ? EFC(E_COEF, adr[u] + 2 * k) : 0.f;
+    }
+#pragma unroll
+    for (int u = 0; u < 2; u++) {
+      const int c = cb + u * TEAM;
+      if (c >= ncon) continue;
+      float fb[4] = {0.f, 0.f, 0.f, 0.f};
+      if (adr[u] >= 0) {
+        if (dim[u] == 1) fb[0] = fr[u][0];
+        else
+#pragma unroll
+          for (int k = 1; k < 4; k++)
+            if (k < dim[u]) { const float fp = fr[u][2 * (k - 1)], fm = fr[u][2 * (k - 1) + 1]; fb[0] += fp + fm; fb[k] = mu[u][k - 1] * (fp - fm); }
+      }
+      for (int k = 0; k < nb; k++) bf[c * nb + k] = fb[k];
+    }
   }
   TSYNC();
   CFT(17);

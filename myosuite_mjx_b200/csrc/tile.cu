@@ -969,10 +969,14 @@ __device__ __noinline__ int newtonTile(int slot, SP sm, Tm t, const NewtonMem& M
   TICK(1);
   int iter = 0, pass = 0;   // pass: Newton passes of the tile so far (tile-uniform)
   bool active = nefc > 0;
+  // Rows and contacts of the worlds that are still iterating: a world that has converged drops out of every per-row and
+  // per-contact loop of the later passes (their trip counts are per lane), so a pass that only serves the tile's stragglers
+  // runs to THEIR row counts and loads only their lines.
+  int nefcA = nefc, nconA = ncon;
   const int lsmax = D.ls_iterations;
   for (;;) {
     // gradient and termination tests
-    constraintForce(slot, sm, t, ncon, nefc, tmp);
+    constraintForce(slot, sm, t, nconA, nefcA, tmp);
     TICK(15);
     float gg[2] = {0.f, 0.f};
     TFOR(k, nv) {
@@ -987,7 +991,8 @@ __device__ __noinline__ int newtonTile(int slot, SP sm, Tm t, const NewtonMem& M
     if (active && iter >= D.iterations) { *status |= MYO_WORLD_SOLVER_MAXITER; active = false; }
     TICK(2);
     if (!__ballot_sync(lmask, active)) break;   // the tile is done when its slowest world is
-    if (pass == 0) { hessianAssemble(slot, sm, t, M.H, ncon, nconT, nefc); TICK(3); } else { hessianUpdate(slot, sm, t, M.H, nefc, M.grad, M.Mv); TICK(4); }   // (grad, Mv: free between the gradient and the solve)
+    if (!active) { nefcA = 0; nconA = 0; }
+    if (pass == 0) { hessianAssemble(slot, sm, t, M.H, ncon, nconT, nefc); TICK(3); } else { hessianUpdate(slot, sm, t, M.H, nefcA, M.grad, M.Mv); TICK(4); }   // (grad, Mv: free between the gradient and the solve)
     choleskyTile(nv, M.H, M.Hd, t);
     TICK(5);
     pass++;
@@ -1002,14 +1007,14 @@ __device__ __noinline__ int newtonTile(int slot, SP sm, Tm t, const NewtonMem& M
     mulMsparse(slot, sm + L.qM, search, Mv, t);
     TICK(12);
     auto bx = sm + L.basev;
-    baseMul(slot, sm, t, ncon, search, bx);
+    baseMul(slot, sm, t, nconA, search, bx);
     TSYNC();
     TICK(13);
-    for (int rb = t.tl; rb < nefc; rb += RB * nw) {
+    for (int rb = t.tl; rb < nefcA; rb += RB * nw) {
       float jv[RB];
-      rowMulBatch(slot, sm, rb, nw, nefc, search, bx, jv);
+      rowMulBatch(slot, sm, rb, nw, nefcA, search, bx, jv);
 #pragma unroll
-      for (int u = 0; u < RB; u++) if (rb + u * nw < nefc) EFC(E_JV, rb + u * nw) = jv[u];
+      for (int u = 0; u < RB; u++) if (rb + u * nw < nefcA) EFC(E_JV, rb + u * nw) = jv[u];
     }
     float g12[2] = {0.f, 0.f};
     TFOR(k, nv) { g12[0] = fmaf(search[k], Ma[k] - smooth[k], g12[0]); g12[1] = fmaf(0.5f * search[k], Mv[k], g12[1]); }
@@ -1019,8 +1024,8 @@ __device__ __noinline__ int newtonTile(int slot, SP sm, Tm t, const NewtonMem& M
     const float gtol = D.tolerance * D.ls_tolerance * sn / scale;
     int lsiter = 0;
     LsPt p0, p1;
-    { const float a0 = 0.f; lsEvalTile<1>(slot, sm, t, nefc, &a0, qg, gtol, &p0); lsiter++; }
-    { const float a1 = p0.alpha - p0.d0 / p0.d1; lsEvalTile<1>(slot, sm, t, nefc, &a1, qg, gtol, &p1); lsiter++; }
+    { const float a0 = 0.f; lsEvalTile<1>(slot, sm, t, nefcA, &a0, qg, gtol, &p0); lsiter++; }
+    { const float a1 = p0.alpha - p0.d0 / p0.d1; lsEvalTile<1>(slot, sm, t, nefcA, &a1, qg, gtol, &p1); lsiter++; }
     if (p0.cost < p1.cost) p1 = p0;
     bool done = !active || fabsf(p1.d0) < p1.tol;
     const float dir = p1.d0 < 0.f ? 1.f : -1.f;
@@ -1029,7 +1034,7 @@ __device__ __noinline__ int newtonTile(int slot, SP sm, Tm t, const NewtonMem& M
       const bool want = !done && p1.d0 * dir <= -p1.tol && lsiter < lsmax;
       if (!__ballot_sync(lmask, want)) break;
       const float a = want ? p1.alpha - p1.d0 / p1.d1 : 0.f;
-      LsPt pn; lsEvalTile<1>(slot, sm, t, nefc, &a, qg, gtol, &pn);
+      LsPt pn; lsEvalTile<1>(slot, sm, t, nefcA, &a, qg, gtol, &pn);
       if (want) { p2 = p1; have2 = true; p1 = pn; lsiter++; if (fabsf(p1.d0) < p1.tol) done = true; }
     }
     bool refine = !done && lsiter < lsmax && have2;
@@ -1039,7 +1044,7 @@ __device__ __noinline__ int newtonTile(int slot, SP sm, Tm t, const NewtonMem& M
       if (!__ballot_sync(lmask, want)) break;
       const float ca[3] = {want ? lo.alpha - lo.d0 / lo.d1 : 0.f, want ? hi.alpha - hi.d0 / hi.d1 : 0.f, want ? 0.5f * (lo.alpha + hi.alpha) : 0.f};
       LsPt cand[3];
-      lsEvalTile<3>(slot, sm, t, nefc, ca, qg, gtol, cand);
+      lsEvalTile<3>(slot, sm, t, nefcA, ca, qg, gtol, cand);
       if (want) {
         lsiter += 3;
         bool moved = false, hit = false;
@@ -1064,17 +1069,17 @@ __device__ __noinline__ int newtonTile(int slot, SP sm, Tm t, const NewtonMem& M
     if (active && alpha == 0.f) active = false;
     if (active) TFOR(k, nv) { qacc[k] = fmaf(alpha, search[k], qacc[k]); Ma[k] = fmaf(alpha, Mv[k], Ma[k]); }
     float gc[2] = {0.f, 0.f};
-    for (int rb = t.tl; rb < nefc; rb += RB * nw) {
+    for (int rb = t.tl; rb < nefcA; rb += RB * nw) {
       float jarv[RB], jvv[RB], Drv[RB]; int d0v[RB];
 #pragma unroll
       for (int u = 0; u < RB; u++) {
-        const int r = rb + u * nw; const bool ok = r < nefc;
+        const int r = rb + u * nw; const bool ok = r < nefcA;
         jarv[u] = ok ? EFC(E_JAR, r) : 0.f; jvv[u] = ok ? EFC(E_JV, r) : 0.f; Drv[u] = ok ? EFC(E_D, r) : 0.f; d0v[u] = ok ? EFCI(E_DESC0, r) : ROW_CON;
       }
 #pragma unroll
       for (int u = 0; u < RB; u++) {
         const int r = rb + u * nw;
-        if (r < nefc) {
+        if (r < nefcA) {
           float jar = jarv[u], flip = 0.f;
           if (active) {
             const float old = jar;
