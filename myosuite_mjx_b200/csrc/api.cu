@@ -7,6 +7,7 @@
 #include <cstring>
 #include <algorithm>
 #include <atomic>
+#include <functional>
 #include <mutex>
 #include <string>
 #include <vector>
@@ -182,7 +183,7 @@ void myo_batch_destroy(myo_batch* b) {
   cudaSetDevice(b->model->device);
   for (void* p : b->owned) cudaFree(p);
   for (int i = 0; i < 4; i++) if (b->side[i]) { cudaStreamSynchronize((cudaStream_t)b->side[i]); cudaStreamDestroy((cudaStream_t)b->side[i]); }
-  for (int i = 0; i < 6; i++) if (b->ev[i]) cudaEventDestroy((cudaEvent_t)b->ev[i]);
+  for (int i = 0; i < 8; i++) if (b->ev[i]) cudaEventDestroy((cudaEvent_t)b->ev[i]);
   releaseSlot(b->slot);
   delete b;
 }
@@ -253,7 +254,7 @@ static int launchPhases(myo_batch* b, int nsub, int forward_only, const int32_t*
     static const bool prio = !(getenv("MYO_PRIORITY") && atoi(getenv("MYO_PRIORITY")) == 0);   // developer knob
     const int pr[4] = {prio ? greatest : least, prio ? std::min(least, greatest + 1) : least, prio ? std::min(least, greatest + 2) : least, least};
     for (int i = 0; i < 4; i++) { cudaStream_t cs; if (cudaStreamCreateWithPriority(&cs, cudaStreamNonBlocking, pr[i]) != cudaSuccess) return fail(MYO_ERR_CUDA, "side stream creation failed"); b->side[i] = cs; }
-    for (int i = 0; i < 6; i++) { cudaEvent_t e; if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess) return fail(MYO_ERR_CUDA, "event creation failed"); b->ev[i] = e; }
+    for (int i = 0; i < 8; i++) { cudaEvent_t e; if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess) return fail(MYO_ERR_CUDA, "event creation failed"); b->ev[i] = e; }
   }
   const bool posvel = forward_only == 2;
   const int nloop = forward_only ? 1 : nsub;
@@ -272,13 +273,15 @@ static int launchPhases(myo_batch* b, int nsub, int forward_only, const int32_t*
   };
   bool ok = true;
   // mj_collision = broad phase + closed-form pairs, the listed convex pairs one per lane, ordered compaction
-  auto collide = [&](int fslot) {
+  auto collide = [&](int fslot, int mark = 0, const std::function<void()>& at_mark = nullptr) {   // at_mark(): after kernel `mark` of the chain (1 = broad phase, 2 = convex narrow phase)
     bool r = true;
     r &= tile(MYO_K_COLLIDE, fslot, 0) == 0;
+    if (mark == 1) at_mark();
     if (b->D.npair > 0) {
       if (b->D.nmprpair > 0 || b->F.p[MYO_F_GEOM_TYPE_OVR]) r &= tile(MYO_K_COLLIDE_MPR, fslot, 0) == 0;
+      if (mark == 2) at_mark();
       r &= tile(MYO_K_COLLIDE_COMPACT, fslot, 0) == 0;
-    }
+    } else if (mark == 2) at_mark();
     return r;
   };
   static const int debug_stop = getenv("MYO_DEBUG_STOP") ? atoi(getenv("MYO_DEBUG_STOP")) : -1;   // developer knob: end the pipeline after this many kernels
@@ -301,7 +304,8 @@ static int launchPhases(myo_batch* b, int nsub, int forward_only, const int32_t*
       for (int i = 0; i < 4; i++) ok &= cudaStreamWaitEvent(S(i), E(0), 0) == cudaSuccess;
       // output stream (lowest priority): the position stage's fields now, the contact / constraint records once the rows exist
       static const int ndelay = getenv("MYO_DELAY") ? atoi(getenv("MYO_DELAY")) : 1;   // developer knob
-      if (posout) {
+      static const int posout_after = getenv("MYO_POSOUT_AFTER") ? atoi(getenv("MYO_POSOUT_AFTER")) : 0;   // developer knob: 0 = after kin (best), 1 = after collide (+0.4 %), 2 = after collideMpr (+1.4 %)
+      if (posout && posout_after == 0) {
         for (int i = 0; i < 2 * ndelay; i++) { g_launches++; ok &= myo_nop_launch(b->side[3]) == 0; }   // (behind tendon / inertia, see below)
         cur = b->side[3]; ok &= tile(MYO_K_POSOUT, fslot, 0) == 0;
       }
@@ -313,15 +317,26 @@ static int launchPhases(myo_batch* b, int nsub, int forward_only, const int32_t*
           void* keep = cur; cur = b->side[3]; ok &= tile(MYO_K_CONOUT, fslot, 0) == 0; cur = keep;
         }
       };
-      cur = b->side[0]; ok &= collide(fslot);
-      if (makecon_early) rows(S(0));
-      ok &= cudaEventRecord(E(1), S(0)) == cudaSuccess;
+      // the position outputs start behind the broad phase: the convex narrow phase (201 registers per thread) then takes the
+      // SM slots the first kernels free before the output kernel does (stream priorities decide between waiting CTAs only)
+      int collide_mark = posout ? posout_after : 0;
+      cur = b->side[0]; ok &= collide(fslot, collide_mark, [&]() {
+        ok &= cudaEventRecord(E(7), S(0)) == cudaSuccess && cudaStreamWaitEvent(S(3), E(7), 0) == cudaSuccess;
+        void* keep = cur; cur = b->side[3]; ok &= tile(MYO_K_POSOUT, fslot, 0) == 0; cur = keep;
+      });
       for (int i = 0; i < ndelay; i++) { g_launches += 2; ok &= myo_nop_launch(b->side[1]) == 0 && myo_nop_launch(b->side[2]) == 0; }
       cur = b->side[1]; ok &= tile(MYO_K_TENDON, fslot, 0) == 0;
+      if (posout) {   // ten_length, ten_J, path points: on the output stream, behind the tendon stage
+        ok &= cudaEventRecord(E(6), S(1)) == cudaSuccess && cudaStreamWaitEvent(S(3), E(6), 0) == cudaSuccess;
+        cur = b->side[3]; ok &= tile(MYO_K_TENOUT, fslot, 0) == 0; cur = b->side[1];
+      }
       cur = b->side[2]; ok &= tile(MYO_K_INERTIA, fslot, forward_only ? 0 : 1) == 0;
       ok &= cudaEventRecord(E(2), S(2)) == cudaSuccess && cudaStreamWaitEvent(S(1), E(2), 0) == cudaSuccess;
       cur = b->side[1]; ok &= tile(MYO_K_VELACT, fslot, 0) == 0;
       ok &= cudaEventRecord(E(5), S(1)) == cudaSuccess;
+      cur = b->side[0];   // (after the tendon branch in host order: the output stream then holds posout, tenout, conout in that order)
+      if (makecon_early) rows(S(0));
+      ok &= cudaEventRecord(E(1), S(0)) == cudaSuccess;
       cur = stream;
       ok &= cudaStreamWaitEvent(main, E(1), 0) == cudaSuccess && cudaStreamWaitEvent(main, E(5), 0) == cudaSuccess;
       if (!makecon_early) rows(main);
@@ -338,6 +353,7 @@ static int launchPhases(myo_batch* b, int nsub, int forward_only, const int32_t*
     }
     if (posout) { ok &= tile(MYO_K_POSOUT, fslot, 0) == 0; STOP_HERE(); }
     ok &= tile(MYO_K_TENDON, fslot, 0) == 0; STOP_HERE();
+    if (posout) { ok &= tile(MYO_K_TENOUT, fslot, 0) == 0; STOP_HERE(); }
     if (!posvel) {
       ok &= tile(MYO_K_INERTIA, fslot, forward_only ? 0 : 1) == 0; STOP_HERE();
       ok &= collide(fslot); STOP_HERE();

@@ -592,8 +592,8 @@ __device__ __noinline__ float wrapGeom(f3 x0, f3 x1, f3 gpos, const float* gmat,
 __device__ __noinline__ void tendons(int slot, int fslot, SP sm, Tm t, World W) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L; const FieldPtrs& F = tP[fslot].F;
   void* wx = F.p[MYO_F_WRAP_XPOS]; void* wo = F.p[MYO_F_WRAP_OBJ]; void* wa = F.p[MYO_F_TEN_WRAPADR]; void* wn = F.p[MYO_F_TEN_WRAPNUM];
-  const bool wrout = wx || wo || wa || wn;                 // path points written here (the wide-output kernel is off)
-  const bool wantw = wrout || (L.wantw && fslot == slot);   // path points requested: keep tangent points and wrap counts
+  const bool wrout = wx || wo || wa || wn;                 // path points requested: tendonOutputs (tenoutKernel) writes them
+  const bool wantw = wrout;                                 // ... from the tangent points and unit sites kept here
   TFOR(uo, D.nunit) {
     const int u = D.unit_order[uo];
     const int s0 = D.unit_s0[u], s1 = D.unit_s1[u], g = D.unit_geom[u];
@@ -649,57 +649,7 @@ __device__ __noinline__ void tendons(int slot, int fslot, SP sm, Tm t, World W) 
     sm[L.tenlen + k] = acc;
   }
   TSYNC();
-  if (wantw) {
-    // Path points in mj_tendon's order: per unit its first site, the two tangent points if it wraps (wrap_obj = geom id),
-    // the last site at a tendon / pulley-branch end (wrap_obj -1), a marker per pulley (wrap_obj -2, position unset = 0).
-    // Offsets = static offsets + 2 x (wrapping units before the item); entries past the last point are zero.
-    const int ngu = D.ngunit;
-    if (t.tl == 0) {
-      int acc = 0;
-      for (int k = 0; k < ngu; k++) { sm[L.gpre + k] = __int_as_float(acc); acc += sm[L.uwrap + D.gunit[k]] != 0.f ? 1 : 0; }
-      sm[L.gpre + ngu] = __int_as_float(acc);
-    }
-    TSYNC();
-  }
-  if (wrout) {
-    const int ngu = D.ngunit;
-    auto put = [&](int i, f3 p, int obj) {
-      if (wx) { float* o = (float*)wx + (size_t)(3 * i) * W.nw + W.w; o[0] = p.x; o[W.nw] = p.y; o[2 * W.nw] = p.z; }
-      if (wo) OUTI(wo, i) = obj;
-    };
-    TFOR(u, D.nunit) {
-      const int go = D.unit_gord[u], g = D.unit_geom[u];
-      const bool wrapped = sm[L.uwrap + u] != 0.f;
-      const int off = D.unit_woff[u] + 2 * __float_as_int(sm[L.gpre + go]);
-      put(off, ld3(sm + L.upts + 6 * u), -1);
-      if (wrapped) { auto wp = sm + L.uwpt + 6 * go; put(off + 1, ld3(wp), g); put(off + 2, ld3(wp + 3), g); }
-      if (D.unit_end[u]) put(off + (wrapped ? 3 : 1), ld3(sm + L.upts + 6 * u + 3), -1);
-    }
-    TFOR(i, D.npulley) put(D.pul_off[i] + 2 * __float_as_int(sm[L.gpre + D.pul_gord[i]]), mk3(0.f, 0.f, 0.f), -2);
-    TFOR(k, D.nten) {
-      const int g0 = __float_as_int(sm[L.gpre + D.ten_gord[k]]), g1 = __float_as_int(sm[L.gpre + D.ten_gord[k + 1]]);
-      if (wa) OUTI(wa, k) = D.ten_woff[k] + 2 * g0;
-      if (wn) OUTI(wn, k) = D.ten_woff[k + 1] - D.ten_woff[k] + 2 * (g1 - g0);
-    }
-    // entries past the last point: only those a previous step can have written (all geom units wrapped); the rest of the
-    // buffer keeps the zeros it was given when it was bound (api.cu)
-    for (int i = D.ten_woff[D.nten] + 2 * __float_as_int(sm[L.gpre + ngu]) + t.tl; i < D.ten_woff[D.nten] + 2 * ngu; i += TEAM) put(i, mk3(0.f, 0.f, 0.f), 0);
-  }
-  void* tl = F.p[MYO_F_TEN_LENGTH]; void* tj = F.p[MYO_F_TEN_J];
-  if (tl) TFOR(k, D.nten) OUTF(tl, k) = sm[L.tenlen + k];
-  if (tj) {
-    TFOR(k, D.nten) {   // dense row = zeros with the sparse entries (sorted by dof) merged in
-      int q = D.ten_nzstart[k];
-      const int qend = D.ten_nzstart[k + 1];
-      for (int i = 0; i < D.nv; i++) {
-        float v = 0.f;
-        if (q < qend && D.nz_dof[q] == i) { v = sm[L.tenJ + q]; q++; }
-        OUTF(tj, k * D.nv + i) = v;
-      }
-    }
-  }
 }
-
 // ------------------------------------------------------------------------------------------ inertia: mj_crb, mj_factorM, mj_solveM
 // sparse L^T D L in place over the dof-tree pattern; one precomputed multiply-subtract list per column
 __device__ __noinline__ void factorLDL(int slot, SP LD, SP dinv, Tm t) {

@@ -13,7 +13,7 @@ void myo_make_layout(DevModel& D, int nconmax_req, int njmax_req, SmemLayout& L)
 
 #define MYO_PARAM_SLOTS 16   // live batches per process: one constant-memory parameter slot each (17 x ~2.3 KB of the 64 KB)
 // The kernels of the pipeline (tile.cu, lane = world): one entry per phase
-enum { MYO_K_KIN = 0, MYO_K_TENDON, MYO_K_INERTIA, MYO_K_COLLIDE, MYO_K_VELACT, MYO_K_FINISH, MYO_K_CONOUT, MYO_K_NEWTON, MYO_K_COLLIDE_MPR, MYO_K_COLLIDE_COMPACT, MYO_K_MAKECON, MYO_K_POSOUT };
+enum { MYO_K_KIN = 0, MYO_K_TENDON, MYO_K_INERTIA, MYO_K_COLLIDE, MYO_K_VELACT, MYO_K_FINISH, MYO_K_CONOUT, MYO_K_NEWTON, MYO_K_COLLIDE_MPR, MYO_K_COLLIDE_COMPACT, MYO_K_MAKECON, MYO_K_POSOUT, MYO_K_TENOUT };
 enum { MYO_KIN_LOAD = 1, MYO_KIN_RESET = 2, MYO_KIN_CHECK = 4 };                 // flags of MYO_K_KIN
 enum { MYO_FIN_EULER = 1, MYO_FIN_STATE = 2, MYO_FIN_WARM = 4, MYO_FIN_ACC = 8 };  // flags of MYO_K_FINISH
 int myo_tile_upload(int slot, const DevModel& D, const SmemLayout& L, const FieldPtrs& F, const TileAux& X, void* stream);
@@ -40,7 +40,7 @@ struct myo_batch {
   // the phases that depend only on the kinematics (tendon, inertia, collide) and the two tails of a step (conout, finish) run
   // concurrently: two library-owned side streams fork from and join the caller's stream with events (graph-capturable)
   void* side[4] = {nullptr, nullptr, nullptr, nullptr};   // collision chain (high priority), tendon -> velact, inertia, records out (low priority)
-  void* ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  void* ev[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
   std::vector<void*> owned;
 };
 

@@ -401,6 +401,73 @@ __device__ __noinline__ TileScan tileScan(Tm t, int cnt) {
   __syncthreads();
   return r;
 }
+// The tendon stage's output fields (ten_length, dense ten_J, the path points), from what tendons() left in the scratch: their
+// own launch on the output stream (tenoutKernel) -- a quarter of the tendon kernel's time was these stores, and velact and the
+// solver wait for that kernel.
+__device__ __noinline__ void tendonOutputs(int slot, int fslot, SP sm, Tm t, World W) {
+  const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L; const FieldPtrs& F = tP[fslot].F;
+  void* wx = F.p[MYO_F_WRAP_XPOS]; void* wo = F.p[MYO_F_WRAP_OBJ]; void* wa = F.p[MYO_F_TEN_WRAPADR]; void* wn = F.p[MYO_F_TEN_WRAPNUM];
+  const bool wrout = wx || wo || wa || wn;
+  if (wrout) {
+    // Path points in mj_tendon's order: per unit its first site, the two tangent points if it wraps (wrap_obj = geom id),
+    // the last site at a tendon / pulley-branch end (wrap_obj -1), a marker per pulley (wrap_obj -2, position unset = 0).
+    // Offsets = static offsets + 2 x (wrapping units before the item); entries past the last point are zero.
+    // gpre[k] = wrapping units among the first k geom units: counted by per-warp chunks, prefix over the warps
+    const int ngu = D.ngunit;
+    const int chunk = (ngu + TEAM - 1) / TEAM, k0 = min(ngu, t.tl * chunk), k1 = min(ngu, k0 + chunk);
+    int cnt = 0;
+    for (int k = k0; k < k1; k++) cnt += sm[L.uwrap + D.gunit[k]] != 0.f ? 1 : 0;
+    const TileScan sc = tileScan(t, cnt);
+    int acc = sc.off;
+    for (int k = k0; k < k1; k++) { sm[L.gpre + k] = __int_as_float(acc); acc += sm[L.uwrap + D.gunit[k]] != 0.f ? 1 : 0; }
+    if (t.tl == 0) sm[L.gpre + ngu] = __int_as_float(sc.total);
+    TSYNC();
+    auto put = [&](int i, f3 p, int obj) {
+      if (wx) { OUTF(wx, 3 * i) = p.x; OUTF(wx, 3 * i + 1) = p.y; OUTF(wx, 3 * i + 2) = p.z; }
+      if (wo) OUTI(wo, i) = obj;
+    };
+    TFOR(u, D.nunit) {
+      const int go = D.unit_gord[u], g = D.unit_geom[u];
+      const bool wrapped = sm[L.uwrap + u] != 0.f;
+      const int off = D.unit_woff[u] + 2 * __float_as_int(sm[L.gpre + go]);
+      put(off, ld3(sm + L.upts + 6 * u), -1);
+      if (wrapped) { auto wp = sm + L.uwpt + 6 * go; put(off + 1, ld3(wp), g); put(off + 2, ld3(wp + 3), g); }
+      if (D.unit_end[u]) put(off + (wrapped ? 3 : 1), ld3(sm + L.upts + 6 * u + 3), -1);
+    }
+    TFOR(i, D.npulley) put(D.pul_off[i] + 2 * __float_as_int(sm[L.gpre + D.pul_gord[i]]), mk3(0.f, 0.f, 0.f), -2);
+    TFOR(k, D.nten) {
+      const int g0 = __float_as_int(sm[L.gpre + D.ten_gord[k]]), g1 = __float_as_int(sm[L.gpre + D.ten_gord[k + 1]]);
+      if (wa) OUTI(wa, k) = D.ten_woff[k] + 2 * g0;
+      if (wn) OUTI(wn, k) = D.ten_woff[k + 1] - D.ten_woff[k] + 2 * (g1 - g0);
+    }
+    // entries past the last point: only those a previous step can have written (all geom units wrapped); the rest of the
+    // buffer keeps the zeros it was given when it was bound (api.cu)
+    for (int i = D.ten_woff[D.nten] + 2 * __float_as_int(sm[L.gpre + ngu]) + t.tl; i < D.ten_woff[D.nten] + 2 * ngu; i += TEAM) put(i, mk3(0.f, 0.f, 0.f), 0);
+  }
+  void* tl = F.p[MYO_F_TEN_LENGTH]; void* tj = F.p[MYO_F_TEN_J];
+  if (tl) TFOR(k, D.nten) OUTF(tl, k) = sm[L.tenlen + k];
+  if (tj) {
+    TFOR(k, D.nten) {   // dense row = zeros with the sparse entries (sorted by dof) merged in
+      int q = D.ten_nzstart[k];
+      const int qend = D.ten_nzstart[k + 1];
+      for (int i = 0; i < D.nv; i++) {
+        float v = 0.f;
+        if (q < qend && D.nz_dof[q] == i) { v = sm[L.tenJ + q]; q++; }
+        OUTF(tj, k * D.nv + i) = v;
+      }
+    }
+  }
+}
+
+#ifndef MINB_TENOUT
+#define MINB_TENOUT 3
+#endif
+__global__ void __launch_bounds__(32 * MAXW, MINB_TENOUT) tenoutKernel(int slot, int fslot, int nworld, const int* __restrict__ mask, float* __restrict__ scratch) {
+  Timeline tline(slot, MYO_K_TENOUT);
+  Ctx c = tileCtx(slot, nworld, mask, scratch);
+  if (!c.live) return;
+  tendonOutputs(slot, fslot, c.sm, c.t, c.W);
+}
 __device__ __noinline__ int tileMinI(Tm t, int v) {
   __shared__ int sc[MAXW][32];
   const int lane = threadIdx.x & 31;
@@ -1331,10 +1398,13 @@ int myo_tile_launch(int kernel, int slot, int fslot, int nworld, const int* mask
   // Measured on 8192 MyoHand worlds (profiles/r2_warps_per_tile.txt): every kernel is bound by the dependent-instruction
   // latency of its warps, and a tile's warps split its items, so more warps per tile shorten the chains -- until the
   // register file (two tiles per SM must stay resident: 256 tiles on 148 SMs) forces spills.  12 is the sweet spot for the
-  // solver (8: +6.6 % step time, 10: +3.9 %, 16 at <= 64 registers: +1.8 %); the tendon phase prefers 8.
-  static const int nwKin = envInt("MYO_NW_KIN", 12), nwTen = envInt("MYO_NW_TEN", 8), nwIne = envInt("MYO_NW_INE", 8),
+  // solver (8: +6.6 % step time, 10: +3.9 %, 16 at <= 64 registers: +1.8 %).  With the 56-register caps of the phase-2 kernels
+  // (three CTAs per SM) 12 warps is also best for tendon, inertia and the output kernels (8: +2 % step time, +4 % in the
+  // contact-poor first steps).
+  static const int nwKin = envInt("MYO_NW_KIN", 12), nwTen = envInt("MYO_NW_TEN", 12), nwIne = envInt("MYO_NW_INE", 12),
                    nwCol = envInt("MYO_NW_COL", 12), nwVel = envInt("MYO_NW_VEL", 12), nwFin = envInt("MYO_NW_FIN", 8),
-                   nwOut = envInt("MYO_NW_OUT", 8), yOut = envInt("MYO_Y_OUT", 4), nwNew = envInt("MYO_NW_NEWTON", 12), nwMak = envInt("MYO_NW_MAKECON", 12), nwPos = envInt("MYO_NW_POSOUT", 8);
+                   nwOut = std::min(8, envInt("MYO_NW_OUT", 8)), yOut = envInt("MYO_Y_OUT", 4), nwNew = envInt("MYO_NW_NEWTON", 12),
+                   nwMak = envInt("MYO_NW_MAKECON", 12), nwPos = envInt("MYO_NW_POSOUT", 12);
   const int tiles = (nworld + 31) / 32;
   cudaStream_t st = (cudaStream_t)stream;
   switch (kernel) {
@@ -1362,6 +1432,7 @@ int myo_tile_launch(int kernel, int slot, int fslot, int nworld, const int* mask
       }
       newtonKernel<<<tiles, 32 * nwNew, shmem, st>>>(slot, fslot, nworld, mask, flags & 1, use_smem, (flags & 32) ? ((flags >> 1) & 15) : -1, scratch);
     } break;
+    case MYO_K_TENOUT: tenoutKernel<<<tiles, 32 * nwPos, 0, st>>>(slot, fslot, nworld, mask, scratch); break;
     case MYO_K_POSOUT: posoutKernel<<<tiles, 32 * nwPos, 0, st>>>(slot, fslot, nworld, mask, scratch); break;
     case MYO_K_MAKECON: makeconKernel<<<tiles, 32 * nwMak, 0, st>>>(slot, nworld, mask, scratch); break;
     case MYO_K_CONOUT: conoutKernel<<<dim3(tiles, yOut), 32 * nwOut, 0, st>>>(slot, fslot, nworld, mask, scratch); break;

@@ -17,7 +17,7 @@ def run(n0, n1):
         if i % 10 == 0: d.storage("ctrl").copy_(partition.ctrl_hash_torch(m.nu, 0, nw, 1234, i // 10, "cuda"))
         mjx.step(model, d, 1)
 run(0, A)
-names = ["kin", "tendon", "inertia", "collide", "velact", "finish", "conout", "newton", "collideMpr", "collideCompact", "makecon", "posout"]
+names = ["kin", "tendon", "inertia", "collide", "velact", "finish", "conout", "newton", "collideMpr", "collideCompact", "makecon", "posout", "tenout"]
 buf = (ctypes.c_ulonglong * 64)()
 L.myo_debug_timeline(d._h, buf)
 acc = np.zeros((len(names), 2)); tot = 0.0
