@@ -330,9 +330,9 @@ static int launchPhases(myo_batch* b, int nsub, int forward_only, const int32_t*
         ok &= cudaEventRecord(E(6), S(1)) == cudaSuccess && cudaStreamWaitEvent(S(3), E(6), 0) == cudaSuccess;
         cur = b->side[3]; ok &= tile(MYO_K_TENOUT, fslot, 0) == 0; cur = b->side[1];
       }
-      cur = b->side[2]; ok &= tile(MYO_K_INERTIA, fslot, forward_only ? 0 : 1) == 0;
+      cur = b->side[2]; ok &= tile(MYO_K_INERTIA, fslot, (forward_only ? 0 : 1) | (b->D.nM << 8)) == 0;
       ok &= cudaEventRecord(E(2), S(2)) == cudaSuccess && cudaStreamWaitEvent(S(1), E(2), 0) == cudaSuccess;
-      cur = b->side[1]; ok &= tile(MYO_K_VELACT, fslot, 0) == 0;
+      cur = b->side[1]; ok &= tile(MYO_K_VELACT, fslot, (b->D.nM + 2 * b->D.nv) << 8) == 0;
       ok &= cudaEventRecord(E(5), S(1)) == cudaSuccess;
       cur = b->side[0];   // (after the tendon branch in host order: the output stream then holds posout, tenout, conout in that order)
       if (makecon_early) rows(S(0));
@@ -355,10 +355,10 @@ static int launchPhases(myo_batch* b, int nsub, int forward_only, const int32_t*
     ok &= tile(MYO_K_TENDON, fslot, 0) == 0; STOP_HERE();
     if (posout) { ok &= tile(MYO_K_TENOUT, fslot, 0) == 0; STOP_HERE(); }
     if (!posvel) {
-      ok &= tile(MYO_K_INERTIA, fslot, forward_only ? 0 : 1) == 0; STOP_HERE();
+      ok &= tile(MYO_K_INERTIA, fslot, (forward_only ? 0 : 1) | (b->D.nM << 8)) == 0; STOP_HERE();
       ok &= collide(fslot); STOP_HERE();
     }
-    ok &= tile(MYO_K_VELACT, fslot, posvel ? 1 : 0) == 0; STOP_HERE();
+    ok &= tile(MYO_K_VELACT, fslot, (posvel ? 1 : 0) | ((b->D.nM + 2 * b->D.nv) << 8)) == 0; STOP_HERE();
     if (posvel) break;
     ok &= tile(MYO_K_MAKECON, fslot, 0) == 0; STOP_HERE();
     if (conout) { ok &= tile(MYO_K_CONOUT, fslot, 0) == 0; STOP_HERE(); }

@@ -143,27 +143,21 @@ __global__ void __launch_bounds__(32 * MAXW, MINB_TENDON) tendonKernel(int slot,
 
 // ------------------------------------------------------------------------------------------ inertia: mj_crb, mj_factorM (+ Euler's M + h B factor)
 __global__ void __launch_bounds__(32 * MAXW, MINB_INERTIA) inertiaKernel(int slot, int fslot, int nworld, const int* __restrict__ mask, int euler,
-                                                     float* __restrict__ scratch) {
-  const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
+                                                     int flags2, float* __restrict__ scratch) {
   Timeline tline(slot, MYO_K_INERTIA);
   Ctx c = tileCtx(slot, nworld, mask, scratch);
   if (!c.live) return;
   SP sm = c.sm; Tm t = c.t;
-  inertia(slot, fslot, sm, t, c.W);
-  if (euler && D.any_damping) {   // mj_Euler's implicit joint damping: factor of M + h diag(damping), used by finishKernel
-    const float h = D.timestep;
-    TSYNC();
-    TFOR(e, D.nM) sm[L.qH + e] = sm[L.qM + e] + (D.M_row[e] == D.M_col[e] ? h * D.dof_damping[D.M_row[e]] : 0.f);
-    TSYNC();
-    factorLDL(slot, sm + L.qH, sm + L.qHinv, t);
-  }
+  extern __shared__ float tileShared[];
+  SP stage; stage.p = (flags2 & 1) ? tileShared + (threadIdx.x & 31) : nullptr;
+  inertia(slot, fslot, sm, t, c.W, stage, euler);
   TSYNC();
   velocityBody(slot, fslot, sm, t, c.W);   // (cdof_dot was inertia()'s scratch up to here)
 }
 
 // ------------------------------------------------------------------------------------------ velact: mj_fwdVelocity, mj_fwdActuation, mj_fwdAcceleration
 __global__ void __launch_bounds__(32 * MAXW, MINB_VELACT) velactKernel(int slot, int fslot, int nworld, const int* __restrict__ mask, int posvel,
-                                                    float* __restrict__ scratch) {
+                                                    int flags2, float* __restrict__ scratch) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
   Timeline tline(slot, MYO_K_VELACT);
   Ctx c = tileCtx(slot, nworld, mask, scratch);
@@ -186,7 +180,9 @@ __global__ void __launch_bounds__(32 * MAXW, MINB_VELACT) velactKernel(int slot,
     }
     return;
   }
-  actuation(slot, fslot, sm, t, W);
+  extern __shared__ float tileShared[];
+  SP stage; stage.p = (flags2 & 1) ? tileShared + (threadIdx.x & 31) : nullptr;
+  actuation(slot, fslot, sm, t, W, stage);
 }
 
 // ------------------------------------------------------------------------------------------ collide: mj_collision
@@ -454,6 +450,25 @@ __device__ __noinline__ void tendonOutputs(int slot, int fslot, SP sm, Tm t, Wor
         float v = 0.f;
         if (q < qend && D.nz_dof[q] == i) { v = sm[L.tenJ + q]; q++; }
         OUTF(tj, k * D.nv + i) = v;
+      }
+    }
+  }
+  // actuator_moment (mj_transmission): needs the tendon rows and the model only
+  const int nu = D.nu, nv = D.nv;
+  void* o;
+  if ((o = F.p[MYO_F_ACTUATOR_MOMENT])) {
+    TFOR(a, nu) {   // dense row = the tendon's sparse row scaled by the gear
+      const int id = D.act_trnid[a];
+      const bool ten = D.act_trntype[a] == 3;
+      int k = ten ? D.ten_nzstart[id] : 0;
+      const int kend = ten ? D.ten_nzstart[id + 1] : 0;
+      const int jd = ten ? -1 : D.jnt_dofadr[id];
+      const float gear = D.act_gear[a];
+      for (int i = 0; i < nv; i++) {
+        float v = 0.f;
+        if (k < kend && D.nz_dof[k] == i) { v = gear * sm[L.tenJ + k]; k++; }
+        if (i == jd) v = gear;
+        OUTF(o, a * nv + i) = v;
       }
     }
   }
@@ -1410,11 +1425,19 @@ int myo_tile_launch(int kernel, int slot, int fslot, int nworld, const int* mask
   switch (kernel) {
     case MYO_K_KIN: kinKernel<<<tiles, 32 * nwKin, 0, st>>>(slot, fslot, nworld, mask, flags, scratch); break;
     case MYO_K_TENDON: tendonKernel<<<tiles, 32 * nwTen, 0, st>>>(slot, fslot, nworld, mask, scratch); break;
-    case MYO_K_INERTIA: inertiaKernel<<<tiles, 32 * nwIne, 0, st>>>(slot, fslot, nworld, mask, flags, scratch); break;
+    case MYO_K_INERTIA: {   // flags: euler | nM << 8; shared memory: two copies of the factor's pattern per lane (<= 48 KB, else the scratch path)
+      const size_t sh = (size_t)2 * (flags >> 8) * 32 * sizeof(float);
+      const int staged = sh > 0 && sh <= 48 * 1024;
+      inertiaKernel<<<tiles, 32 * nwIne, staged ? sh : 0, st>>>(slot, fslot, nworld, mask, flags & 1, staged, scratch);
+    } break;
     case MYO_K_COLLIDE: collideKernel<<<tiles, 32 * nwCol, 0, st>>>(slot, nworld, mask, scratch); break;
     case MYO_K_COLLIDE_MPR: collideMprKernel<<<148 * 4, 128, 0, st>>>(slot, scratch); break;
     case MYO_K_COLLIDE_COMPACT: collideCompactKernel<<<tiles, 32 * nwCol, 0, st>>>(slot, nworld, mask, scratch); break;
-    case MYO_K_VELACT: velactKernel<<<tiles, 32 * nwVel, 0, st>>>(slot, fslot, nworld, mask, flags, scratch); break;
+    case MYO_K_VELACT: {   // flags: posvel | (nM + 2 nv) << 8
+      const size_t sh = (size_t)(flags >> 8) * 32 * sizeof(float);
+      const int staged = sh > 0 && sh <= 48 * 1024;
+      velactKernel<<<tiles, 32 * nwVel, staged ? sh : 0, st>>>(slot, fslot, nworld, mask, flags & 1, staged, scratch);
+    } break;
     case MYO_K_FINISH: finishKernel<<<tiles, 32 * nwFin, 0, st>>>(slot, fslot, nworld, mask, flags, scratch); break;
     case MYO_K_NEWTON: {
       const int nv = flags >> 8;   // the host passes nv in the upper bits (the model lives in constant memory)
