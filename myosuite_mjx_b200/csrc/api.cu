@@ -182,8 +182,8 @@ void myo_batch_destroy(myo_batch* b) {
   if (!b) return;
   cudaSetDevice(b->model->device);
   for (void* p : b->owned) cudaFree(p);
-  for (int i = 0; i < 4; i++) if (b->side[i]) { cudaStreamSynchronize((cudaStream_t)b->side[i]); cudaStreamDestroy((cudaStream_t)b->side[i]); }
-  for (int i = 0; i < 8; i++) if (b->ev[i]) cudaEventDestroy((cudaEvent_t)b->ev[i]);
+  for (int i = 0; i < 5; i++) if (b->side[i]) { cudaStreamSynchronize((cudaStream_t)b->side[i]); cudaStreamDestroy((cudaStream_t)b->side[i]); }
+  for (int i = 0; i < 10; i++) if (b->ev[i]) cudaEventDestroy((cudaEvent_t)b->ev[i]);
   releaseSlot(b->slot);
   delete b;
 }
@@ -252,9 +252,9 @@ static int launchPhases(myo_batch* b, int nsub, int forward_only, const int32_t*
     int least = 0, greatest = 0;
     cudaDeviceGetStreamPriorityRange(&least, &greatest);
     static const bool prio = !(getenv("MYO_PRIORITY") && atoi(getenv("MYO_PRIORITY")) == 0);   // developer knob
-    const int pr[4] = {prio ? greatest : least, prio ? std::min(least, greatest + 1) : least, prio ? std::min(least, greatest + 2) : least, least};
-    for (int i = 0; i < 4; i++) { cudaStream_t cs; if (cudaStreamCreateWithPriority(&cs, cudaStreamNonBlocking, pr[i]) != cudaSuccess) return fail(MYO_ERR_CUDA, "side stream creation failed"); b->side[i] = cs; }
-    for (int i = 0; i < 8; i++) { cudaEvent_t e; if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess) return fail(MYO_ERR_CUDA, "event creation failed"); b->ev[i] = e; }
+    const int pr[5] = {prio ? greatest : least, prio ? std::min(least, greatest + 1) : least, prio ? std::min(least, greatest + 2) : least, least, least};
+    for (int i = 0; i < 5; i++) { cudaStream_t cs; if (cudaStreamCreateWithPriority(&cs, cudaStreamNonBlocking, pr[i]) != cudaSuccess) return fail(MYO_ERR_CUDA, "side stream creation failed"); b->side[i] = cs; }
+    for (int i = 0; i < 10; i++) { cudaEvent_t e; if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess) return fail(MYO_ERR_CUDA, "event creation failed"); b->ev[i] = e; }
   }
   const bool posvel = forward_only == 2;
   const int nloop = forward_only ? 1 : nsub;
@@ -305,7 +305,9 @@ static int launchPhases(myo_batch* b, int nsub, int forward_only, const int32_t*
       // output stream (lowest priority): the position stage's fields now, the contact / constraint records once the rows exist
       static const int ndelay = getenv("MYO_DELAY") ? atoi(getenv("MYO_DELAY")) : 1;   // developer knob
       static const int posout_after = getenv("MYO_POSOUT_AFTER") ? atoi(getenv("MYO_POSOUT_AFTER")) : 0;   // developer knob: 0 = after kin (best), 1 = after collide (+0.4 %), 2 = after collideMpr (+1.4 %)
-      if (posout && posout_after == 0) {
+      // developer knob MYO_OUT_LATE: bit 0 = the tendon outputs, bit 1 = the position outputs start with the solver (stream 4)
+      static const int out_late = getenv("MYO_OUT_LATE") ? atoi(getenv("MYO_OUT_LATE")) : 2;   // 0: +3 % step time, 1: +1 %, 3: +2.7 %
+      if (posout && posout_after == 0 && !(out_late & 2)) {
         for (int i = 0; i < 2 * ndelay; i++) { g_launches++; ok &= myo_nop_launch(b->side[3]) == 0; }   // (behind tendon / inertia, see below)
         cur = b->side[3]; ok &= tile(MYO_K_POSOUT, fslot, 0) == 0;
       }
@@ -319,14 +321,14 @@ static int launchPhases(myo_batch* b, int nsub, int forward_only, const int32_t*
       };
       // the position outputs start behind the broad phase: the convex narrow phase (201 registers per thread) then takes the
       // SM slots the first kernels free before the output kernel does (stream priorities decide between waiting CTAs only)
-      int collide_mark = posout ? posout_after : 0;
+      int collide_mark = posout && !(out_late & 2) ? posout_after : 0;
       cur = b->side[0]; ok &= collide(fslot, collide_mark, [&]() {
         ok &= cudaEventRecord(E(7), S(0)) == cudaSuccess && cudaStreamWaitEvent(S(3), E(7), 0) == cudaSuccess;
         void* keep = cur; cur = b->side[3]; ok &= tile(MYO_K_POSOUT, fslot, 0) == 0; cur = keep;
       });
       for (int i = 0; i < ndelay; i++) { g_launches += 2; ok &= myo_nop_launch(b->side[1]) == 0 && myo_nop_launch(b->side[2]) == 0; }
       cur = b->side[1]; ok &= tile(MYO_K_TENDON, fslot, 0) == 0;
-      if (posout) {   // ten_length, ten_J, path points: on the output stream, behind the tendon stage
+      if (posout && !(out_late & 1)) {   // ten_length, ten_J, path points: on the output stream, behind the tendon stage
         ok &= cudaEventRecord(E(6), S(1)) == cudaSuccess && cudaStreamWaitEvent(S(3), E(6), 0) == cudaSuccess;
         cur = b->side[3]; ok &= tile(MYO_K_TENOUT, fslot, 0) == 0; cur = b->side[1];
       }
@@ -340,6 +342,9 @@ static int launchPhases(myo_batch* b, int nsub, int forward_only, const int32_t*
       cur = stream;
       ok &= cudaStreamWaitEvent(main, E(1), 0) == cudaSuccess && cudaStreamWaitEvent(main, E(5), 0) == cudaSuccess;
       if (!makecon_early) rows(main);
+      if (posout && out_late) {
+        ok &= cudaEventRecord(E(8), main) == cudaSuccess && cudaStreamWaitEvent((cudaStream_t)b->side[4], E(8), 0) == cudaSuccess;
+      }
       const int fin = (forward_only ? 0 : MYO_FIN_EULER) | (last && (!forward_only || do_reset) ? MYO_FIN_STATE : 0) | (last ? MYO_FIN_WARM | MYO_FIN_ACC : 0);
       static const bool fuse_finish = !(getenv("MYO_FUSE_FINISH") && atoi(getenv("MYO_FUSE_FINISH")) == 0);   // developer knob
       ok &= tile(MYO_K_NEWTON, fslot, (forward_only ? 0 : 1) | (fuse_finish ? (fin << 1) | 32 : 0) | (b->D.nv << 8)) == 0;
@@ -348,6 +353,13 @@ static int launchPhases(myo_batch* b, int nsub, int forward_only, const int32_t*
         cur = b->side[3]; ok &= tile(MYO_K_CONOUT, fslot, 0) == 0; cur = stream;
       }
       if (!fuse_finish) ok &= tile(MYO_K_FINISH, fslot, fin) == 0;
+      if (posout && out_late) {
+        cur = b->side[4];
+        if (out_late & 1) ok &= tile(MYO_K_TENOUT, fslot, 0) == 0;
+        if (out_late & 2) ok &= tile(MYO_K_POSOUT, fslot, 0) == 0;
+        cur = stream;
+        ok &= cudaEventRecord(E(9), (cudaStream_t)b->side[4]) == cudaSuccess && cudaStreamWaitEvent(main, E(9), 0) == cudaSuccess;
+      }
       if (conout || posout) ok &= cudaEventRecord(E(4), S(3)) == cudaSuccess && cudaStreamWaitEvent(main, E(4), 0) == cudaSuccess;
       continue;
     }

@@ -39,8 +39,8 @@ struct myo_batch {
   TileAux X;      // work list of the convex narrow phase
   // the phases that depend only on the kinematics (tendon, inertia, collide) and the two tails of a step (conout, finish) run
   // concurrently: two library-owned side streams fork from and join the caller's stream with events (graph-capturable)
-  void* side[4] = {nullptr, nullptr, nullptr, nullptr};   // collision chain (high priority), tendon -> velact, inertia, records out (low priority)
-  void* ev[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  void* side[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};   // collision chain (high priority), tendon -> velact, inertia, records out (low priority)
+  void* ev[10] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
   std::vector<void*> owned;
 };
 
