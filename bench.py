@@ -155,7 +155,7 @@ def run_reference(args, rank, world):
 
 
 WORKLOAD = "MyoHand ({model}.xml, play.py:8) random-ctrl rollout, {nworld} worlds/GPU, dt 0.002, Newton, full mjData written every step"
-KERNELS = "one myo_step = kin, then collide > collideMpr > collideCompact > makecon | tendon > velact | inertia | posout, conout (output stream), then newton (+ mj_Euler tail): 11 kernels + 4 empty ordering launches (csrc/tile.cu, lane = world)"
+KERNELS = "one myo_step = kin, then collide > collideMpr > collideCompact > makecon | tendon > velact | inertia | tenout, conout (output streams), then newton (+ mj_Euler tail) | posout: 12 kernels + 2 empty ordering launches (csrc/tile.cu, lane = world)"
 
 
 def main():

@@ -231,6 +231,9 @@ static int clearPathPoints(myo_batch* b, void* stream) {
 // mj_Euler and the state outputs.  Everything is ordered behind the caller's stream on entry and joined into it on exit, so
 // the call is stream-ordered like a single kernel.  MYO_CONCURRENT=0 (developer knob) or a partial pass (posvel) runs
 // the same kernels in order on the caller's stream.  Inner substeps of a fused launch materialise nothing.
+static inline int ldlTabIntsHost(const DevModel& D) { return (D.ndlevel + 1) + D.nv + (D.nv + 1) + 2 * (D.nM - D.nv) + 2 * D.nv + D.nM; }   // = ldlTabInts (common.cuh)
+// velactKernel's shared-memory request: (nM + 2 nv) floats per lane << 8 | ints of the LDL index tables << 20; 0 = not staged
+static inline int velactStage(const DevModel& D) { const int f = D.nM + 2 * D.nv, ti = ldlTabIntsHost(D); return (f > 0xfff || ti > 0xfff) ? 0 : (f << 8) | (ti << 20); }
 static int launchPhases(myo_batch* b, int nsub, int forward_only, const int32_t* mask, int do_reset, void* stream) {
   int rc;
   if (b->dirty) {
@@ -334,7 +337,7 @@ static int launchPhases(myo_batch* b, int nsub, int forward_only, const int32_t*
       }
       cur = b->side[2]; ok &= tile(MYO_K_INERTIA, fslot, (forward_only ? 0 : 1) | (b->D.nM << 8)) == 0;
       ok &= cudaEventRecord(E(2), S(2)) == cudaSuccess && cudaStreamWaitEvent(S(1), E(2), 0) == cudaSuccess;
-      cur = b->side[1]; ok &= tile(MYO_K_VELACT, fslot, (b->D.nM + 2 * b->D.nv) << 8) == 0;
+      cur = b->side[1]; ok &= tile(MYO_K_VELACT, fslot, velactStage(b->D)) == 0;
       ok &= cudaEventRecord(E(5), S(1)) == cudaSuccess;
       cur = b->side[0];   // (after the tendon branch in host order: the output stream then holds posout, tenout, conout in that order)
       if (makecon_early) rows(S(0));
@@ -347,7 +350,7 @@ static int launchPhases(myo_batch* b, int nsub, int forward_only, const int32_t*
       }
       const int fin = (forward_only ? 0 : MYO_FIN_EULER) | (last && (!forward_only || do_reset) ? MYO_FIN_STATE : 0) | (last ? MYO_FIN_WARM | MYO_FIN_ACC : 0);
       static const bool fuse_finish = !(getenv("MYO_FUSE_FINISH") && atoi(getenv("MYO_FUSE_FINISH")) == 0);   // developer knob
-      ok &= tile(MYO_K_NEWTON, fslot, (forward_only ? 0 : 1) | (fuse_finish ? (fin << 1) | 32 : 0) | (b->D.nv << 8)) == 0;
+      ok &= tile(MYO_K_NEWTON, fslot, (forward_only ? 0 : 1) | (fuse_finish ? (fin << 1) | 32 : 0) | (b->D.nv << 8) | (ldlTabIntsHost(b->D) << 16)) == 0;
       if (conout && conout_late) {
         ok &= cudaEventRecord(E(3), main) == cudaSuccess && cudaStreamWaitEvent(S(3), E(3), 0) == cudaSuccess;
         cur = b->side[3]; ok &= tile(MYO_K_CONOUT, fslot, 0) == 0; cur = stream;
@@ -370,11 +373,11 @@ static int launchPhases(myo_batch* b, int nsub, int forward_only, const int32_t*
       ok &= tile(MYO_K_INERTIA, fslot, (forward_only ? 0 : 1) | (b->D.nM << 8)) == 0; STOP_HERE();
       ok &= collide(fslot); STOP_HERE();
     }
-    ok &= tile(MYO_K_VELACT, fslot, (posvel ? 1 : 0) | ((b->D.nM + 2 * b->D.nv) << 8)) == 0; STOP_HERE();
+    ok &= tile(MYO_K_VELACT, fslot, (posvel ? 1 : 0) | (velactStage(b->D))) == 0; STOP_HERE();
     if (posvel) break;
     ok &= tile(MYO_K_MAKECON, fslot, 0) == 0; STOP_HERE();
     if (conout) { ok &= tile(MYO_K_CONOUT, fslot, 0) == 0; STOP_HERE(); }
-    ok &= tile(MYO_K_NEWTON, fslot, (forward_only ? 0 : 1) | (b->D.nv << 8)) == 0; STOP_HERE();
+    ok &= tile(MYO_K_NEWTON, fslot, (forward_only ? 0 : 1) | (b->D.nv << 8) | (ldlTabIntsHost(b->D) << 16)) == 0; STOP_HERE();
     ok &= tile(MYO_K_FINISH, fslot, (forward_only ? 0 : MYO_FIN_EULER) | (last && (!forward_only || do_reset) ? MYO_FIN_STATE : 0) |
                                         (last ? MYO_FIN_WARM | MYO_FIN_ACC : 0)) == 0;
   }

@@ -684,14 +684,38 @@ __device__ __noinline__ void factorLDL2(int slot, SP LDa, SP dinva, SP LDb, SP d
     TSYNC();
   }
 }
+// The solve's index tables.  Each level step is a chain of dependent table lookups (level -> dof -> entry list -> entry) in
+// front of very little arithmetic; from global memory, with L1 swept by the Jacobian streams, that chain is what the other
+// warps wait for at every level's barrier (66 % barrier stalls).  A kernel that has shared memory to spare copies the tables
+// there once (ldlTabStage, ldlTabInts ints) and the solve reads them at shared-memory latency.
+struct LdlTab { const int *dlvl_start, *dlvl_dofs, *desc_start, *desc_dof, *desc_idx, *dof_Madr, *dof_rowlen, *M_col; };
+__device__ __forceinline__ LdlTab ldlTabGlobal(const DevModel& D) {
+  LdlTab T; T.dlvl_start = D.dlvl_start; T.dlvl_dofs = D.dlvl_dofs; T.desc_start = D.desc_start; T.desc_dof = D.desc_dof; T.desc_idx = D.desc_idx;
+  T.dof_Madr = D.dof_Madr; T.dof_rowlen = D.dof_rowlen; T.M_col = D.M_col; return T;
+}
+__host__ __device__ __forceinline__ int ldlTabInts(int nv, int nM, int ndlevel) { return (ndlevel + 1) + nv + (nv + 1) + 2 * (nM - nv) + 2 * nv + nM; }
+// cooperative copy by the whole CTA; the caller synchronises before the first solve
+// (by the LIVE lanes of the tile's warps: the threads of a partial or masked tile's other lanes have exited)
+__device__ __forceinline__ LdlTab ldlTabStage(const DevModel& D, int* buf, Tm t) {
+  const int nv = D.nv, nd = D.nM - nv;
+  int* p = buf;
+  const unsigned live = __activemask();
+  const int nlive = __popc(live), rank = __popc(live & ((1u << (threadIdx.x & 31)) - 1u));
+  auto put = [&](const int* src, int n) { for (int i = t.tl * nlive + rank; i < n; i += t.nw * nlive) p[i] = src[i]; const int* r = p; p += n; return r; };
+  LdlTab T;
+  T.dlvl_start = put(D.dlvl_start, D.ndlevel + 1); T.dlvl_dofs = put(D.dlvl_dofs, nv); T.desc_start = put(D.desc_start, nv + 1);
+  T.desc_dof = put(D.desc_dof, nd); T.desc_idx = put(D.desc_idx, nd); T.dof_Madr = put(D.dof_Madr, nv); T.dof_rowlen = put(D.dof_rowlen, nv);
+  T.M_col = put(D.M_col, D.nM);
+  return T;
+}
 // x <- (L^T D L)^-1 x, by dof-tree levels
-__device__ __noinline__ void solveLDL(int slot, SP LD, SP dinv, SP x, Tm t) {
+__device__ __noinline__ void solveLDL(int slot, SP LD, SP dinv, SP x, Tm t, const LdlTab& T) {
   const DevModel& D = tP[slot].D;
   for (int l = D.ndlevel - 1; l >= 0; l--) {
-    for (int idx = D.dlvl_start[l] + t.tl; idx < D.dlvl_start[l + 1]; idx += TEAM) {
-      const int j = D.dlvl_dofs[idx];
+    for (int idx = T.dlvl_start[l] + t.tl; idx < T.dlvl_start[l + 1]; idx += TEAM) {
+      const int j = T.dlvl_dofs[idx];
       float acc = x[j];
-      for (int e = D.desc_start[j]; e < D.desc_start[j + 1]; e++) acc = fmaf(-LD[D.desc_idx[e]], x[D.desc_dof[e]], acc);
+      for (int e = T.desc_start[j]; e < T.desc_start[j + 1]; e++) acc = fmaf(-LD[T.desc_idx[e]], x[T.desc_dof[e]], acc);
       x[j] = acc;
     }
     TSYNC();
@@ -699,15 +723,16 @@ __device__ __noinline__ void solveLDL(int slot, SP LD, SP dinv, SP x, Tm t) {
   TFOR(i, D.nv) x[i] *= dinv[i];
   TSYNC();
   for (int l = 1; l < D.ndlevel; l++) {
-    for (int idx = D.dlvl_start[l] + t.tl; idx < D.dlvl_start[l + 1]; idx += TEAM) {
-      const int i = D.dlvl_dofs[idx], a = D.dof_Madr[i], d = D.dof_rowlen[i];
+    for (int idx = T.dlvl_start[l] + t.tl; idx < T.dlvl_start[l + 1]; idx += TEAM) {
+      const int i = T.dlvl_dofs[idx], a = T.dof_Madr[i], d = T.dof_rowlen[i];
       float acc = x[i];
-      for (int q = 1; q < d; q++) acc = fmaf(-LD[a + q], x[D.M_col[a + q]], acc);
+      for (int q = 1; q < d; q++) acc = fmaf(-LD[a + q], x[T.M_col[a + q]], acc);
       x[i] = acc;
     }
     TSYNC();
   }
 }
+__device__ __forceinline__ void solveLDL(int slot, SP LD, SP dinv, SP x, Tm t) { solveLDL(slot, LD, dinv, x, t, ldlTabGlobal(tP[slot].D)); }
 // `stage`: shared memory for 2 nM elements per lane, or null.  The column-by-column factorisations are chains of dependent
 // loads with two barriers per column: on a shared-memory copy they cost a fraction of what they do on the scratch (30 % of
 // this kernel's samples before), and M and Euler's M + h B (euler != 0) share one pass.
@@ -989,10 +1014,11 @@ __device__ __noinline__ void actuation(int slot, int fslot, SP sm, Tm t, World W
   TSYNC();
   if (stage.p) {   // the level-by-level solve on a shared-memory copy of the factor (27 % of this kernel's samples on the scratch)
     SP LD = stage, dinv = stage + D.nM, x = dinv + nv;
+    const LdlTab T = ldlTabStage(D, (int*)(stage.p - (threadIdx.x & 31) + (D.nM + 2 * nv) * SCR), t);   // (the tables follow the lanes' block)
     TFOR(e, D.nM) LD[e] = sm[L.qLD + e];
     TFOR(i, nv) { dinv[i] = sm[L.qLDinv + i]; x[i] = sm[L.qacc_smooth + i]; }
     TSYNC();
-    solveLDL(slot, LD, dinv, x, t);
+    solveLDL(slot, LD, dinv, x, t, T);
     TFOR(i, nv) sm[L.qacc_smooth + i] = x[i];
     TSYNC();
   } else solveLDL(slot, sm + L.qLD, sm + L.qLDinv, sm + L.qacc_smooth, t);

@@ -1208,7 +1208,16 @@ __device__ __noinline__ void finishTile(int slot, int fslot, SP sm, Tm t, World 
     if ((o = Fo.p[MYO_F_QACC])) TFOR(i, nv) OUTF(o, i) = sm[L.qacc + i];
     if ((o = Fo.p[MYO_F_QFRC_CONSTRAINT])) TFOR(i, nv) OUTF(o, i) = sm[L.qfrc_con + i];
     if ((o = Fo.p[MYO_F_QFRC_INVERSE])) TFOR(i, nv) OUTF(o, i) = 0.f;
-    if ((o = Fo.p[MYO_F_EFC_FORCE])) { const int nefc = __float_as_int(sm[L.counts + 1]); TFOR(r, D.njmax) OUTF(o, r) = r < nefc ? EFC(E_FORCE, r) : 0.f; }
+    if ((o = Fo.p[MYO_F_EFC_FORCE])) {
+      const int nefc = __float_as_int(sm[L.counts + 1]);
+      for (int r0 = t.tl; r0 < D.njmax; r0 += 8 * t.nw) {   // (eight loads in flight)
+        float v[8];
+#pragma unroll
+        for (int u = 0; u < 8; u++) v[u] = r0 + u * t.nw < nefc ? EFC(E_FORCE, r0 + u * t.nw) : 0.f;
+#pragma unroll
+        for (int u = 0; u < 8; u++) if (r0 + u * t.nw < D.njmax) OUTF(o, r0 + u * t.nw) = v[u];
+      }
+    }
     if ((o = Fo.p[MYO_F_SOLVER_NITER]) && t.tl == 0) OUTI(o, 0) = __float_as_int(sm[L.counts + 2]);
   }
   if (flags & FIN_EULER) {
@@ -1219,10 +1228,17 @@ __device__ __noinline__ void finishTile(int slot, int fslot, SP sm, Tm t, World 
       // the level-by-level solve is a chain of dependent loads with a barrier per level: run it on a shared-memory copy of
       // the factor (measured: 5 % of the solver kernel's time when it reads the factor from the scratch)
       SP LD = stage, dinv = stage + D.nM; qa = dinv + nv;
-      TFOR(e, D.nM) LD[e] = sm[L.qH + e];
+      const LdlTab T = ldlTabStage(D, (int*)(stage.p - (threadIdx.x & 31) + (D.nM + 2 * nv) * SCR), t);   // (the tables follow the lanes' block)
+      for (int e0 = t.tl; e0 < D.nM; e0 += 8 * t.nw) {   // (eight loads in flight)
+        float v[8];
+#pragma unroll
+        for (int u = 0; u < 8; u++) v[u] = e0 + u * t.nw < D.nM ? sm[L.qH + e0 + u * t.nw] : 0.f;
+#pragma unroll
+        for (int u = 0; u < 8; u++) if (e0 + u * t.nw < D.nM) LD[e0 + u * t.nw] = v[u];
+      }
       TFOR(i, nv) { dinv[i] = sm[L.qHinv + i]; qa[i] = sm[L.smooth + i] + sm[L.qfrc_con + i]; }
       TSYNC();
-      solveLDL(slot, LD, dinv, qa, t);
+      solveLDL(slot, LD, dinv, qa, t, T);
     } else if (D.any_damping) {
       TFOR(i, nv) qa[i] = sm[L.smooth + i] + sm[L.qfrc_con + i];
       TSYNC();
@@ -1300,7 +1316,7 @@ __global__ void __launch_bounds__(32 * MAXW, MINB_MAKECON) makeconKernel(int slo
   const int nefc = makeConstraintTile(slot, sm, t, ncon, nconT, &status);
   if (t.tl == 0) { sm[L.counts + 1] = __int_as_float(nefc); sm[L.wstate + WS_STATUS] = __int_as_float(status); }
 }
-static inline size_t newtonSmemFloats(int nv) { return (size_t)(TRI(nv) + 7 * nv) * 32; }
+static inline size_t newtonSmemFloats(int nv) { return (size_t)(TRI(nv) + 7 * nv) * 32; }   // (+ the LDL solve's index tables, myo_tile_launch)
 #define NEWTON_SMEM_MAX (190 * 1024)   // + ~31 KB of static reduction / scan buffers <= 227 KB per CTA
 __global__ void __launch_bounds__(32 * MAXW, MINB_NEWTON) newtonKernel(int slot, int fslot, int nworld, const int* __restrict__ mask, int check_acc,
                                                     int use_smem, int fin, float* __restrict__ scratch) {
@@ -1433,15 +1449,15 @@ int myo_tile_launch(int kernel, int slot, int fslot, int nworld, const int* mask
     case MYO_K_COLLIDE: collideKernel<<<tiles, 32 * nwCol, 0, st>>>(slot, nworld, mask, scratch); break;
     case MYO_K_COLLIDE_MPR: collideMprKernel<<<148 * 4, 128, 0, st>>>(slot, scratch); break;
     case MYO_K_COLLIDE_COMPACT: collideCompactKernel<<<tiles, 32 * nwCol, 0, st>>>(slot, nworld, mask, scratch); break;
-    case MYO_K_VELACT: {   // flags: posvel | (nM + 2 nv) << 8
-      const size_t sh = (size_t)(flags >> 8) * 32 * sizeof(float);
+    case MYO_K_VELACT: {   // flags: posvel | (nM + 2 nv) << 8 | ints of the LDL index tables << 20
+      const size_t sh = (size_t)((flags >> 8) & 0xfff) * 32 * sizeof(float) + (size_t)(flags >> 20) * sizeof(int);
       const int staged = sh > 0 && sh <= 48 * 1024;
       velactKernel<<<tiles, 32 * nwVel, staged ? sh : 0, st>>>(slot, fslot, nworld, mask, flags & 1, staged, scratch);
     } break;
     case MYO_K_FINISH: finishKernel<<<tiles, 32 * nwFin, 0, st>>>(slot, fslot, nworld, mask, flags, scratch); break;
     case MYO_K_NEWTON: {
-      const int nv = flags >> 8;   // the host passes nv in the upper bits (the model lives in constant memory)
-      size_t shmem = newtonSmemFloats(nv) * sizeof(float);
+      const int nv = (flags >> 8) & 0xff;   // the host passes nv and the size of the LDL index tables in the upper bits (the model lives in constant memory)
+      size_t shmem = newtonSmemFloats(nv) * sizeof(float) + (size_t)(flags >> 16) * sizeof(int);
       const int use_smem = shmem <= NEWTON_SMEM_MAX ? 1 : 0;
       if (!use_smem) shmem = 0;
       static size_t configured[64] = {0};   // per device: largest dynamic shared-memory size opted in to so far
