@@ -652,33 +652,39 @@ __device__ __noinline__ void tendons(int slot, int fslot, SP sm, Tm t, World W) 
 }
 // ------------------------------------------------------------------------------------------ inertia: mj_crb, mj_factorM, mj_solveM
 // sparse L^T D L in place over the dof-tree pattern; one precomputed multiply-subtract list per column
-__device__ __noinline__ void factorLDL(int slot, SP LD, SP dinv, Tm t) {
+// The factorisation's index tables (see LdlTab below: same reason, same staging).
+struct LdlFacTab { const int *ldl_start, *ldl_dst, *ldl_a, *ldl_b, *dof_Madr, *dof_rowlen; };
+__device__ __forceinline__ LdlFacTab ldlFacTabGlobal(const DevModel& D) {
+  LdlFacTab T; T.ldl_start = D.ldl_start; T.ldl_dst = D.ldl_dst; T.ldl_a = D.ldl_a; T.ldl_b = D.ldl_b; T.dof_Madr = D.dof_Madr; T.dof_rowlen = D.dof_rowlen; return T;
+}
+__device__ __noinline__ void factorLDL(int slot, SP LD, SP dinv, Tm t, const LdlFacTab& T) {
   const DevModel& D = tP[slot].D;
   const int nv = D.nv;
   for (int pos = 0; pos < nv; pos++) {
-    const int k = nv - 1 - pos, akk = D.dof_Madr[k];
+    const int k = nv - 1 - pos, akk = T.dof_Madr[k];
     const float inv = 1.f / LD[akk];
-    for (int o = D.ldl_start[pos] + t.tl; o < D.ldl_start[pos + 1]; o += TEAM) LD[D.ldl_dst[o]] -= LD[D.ldl_a[o]] * LD[D.ldl_b[o]] * inv;
+    for (int o = T.ldl_start[pos] + t.tl; o < T.ldl_start[pos + 1]; o += TEAM) LD[T.ldl_dst[o]] -= LD[T.ldl_a[o]] * LD[T.ldl_b[o]] * inv;
     TSYNC();
-    const int d = D.dof_rowlen[k];
+    const int d = T.dof_rowlen[k];
     for (int q = 1 + t.tl; q < d; q += TEAM) LD[akk + q] *= inv;
     if (t.tl == 0) dinv[k] = inv;
     TSYNC();
   }
 }
+__device__ __forceinline__ void factorLDL(int slot, SP LD, SP dinv, Tm t) { factorLDL(slot, LD, dinv, t, ldlFacTabGlobal(tP[slot].D)); }
 // two matrices of the same pattern (M and Euler's M + h B) in one pass over the columns: half the barriers
-__device__ __noinline__ void factorLDL2(int slot, SP LDa, SP dinva, SP LDb, SP dinvb, Tm t) {
+__device__ __noinline__ void factorLDL2(int slot, SP LDa, SP dinva, SP LDb, SP dinvb, Tm t, const LdlFacTab& T) {
   const DevModel& D = tP[slot].D;
   const int nv = D.nv;
   for (int pos = 0; pos < nv; pos++) {
-    const int k = nv - 1 - pos, akk = D.dof_Madr[k];
+    const int k = nv - 1 - pos, akk = T.dof_Madr[k];
     const float inva = 1.f / LDa[akk], invb = 1.f / LDb[akk];
-    for (int o = D.ldl_start[pos] + t.tl; o < D.ldl_start[pos + 1]; o += TEAM) {
-      const int dst = D.ldl_dst[o], ia = D.ldl_a[o], ib = D.ldl_b[o];
+    for (int o = T.ldl_start[pos] + t.tl; o < T.ldl_start[pos + 1]; o += TEAM) {
+      const int dst = T.ldl_dst[o], ia = T.ldl_a[o], ib = T.ldl_b[o];
       LDa[dst] -= LDa[ia] * LDa[ib] * inva; LDb[dst] -= LDb[ia] * LDb[ib] * invb;
     }
     TSYNC();
-    const int d = D.dof_rowlen[k];
+    const int d = T.dof_rowlen[k];
     for (int q = 1 + t.tl; q < d; q += TEAM) { LDa[akk + q] *= inva; LDb[akk + q] *= invb; }
     if (t.tl == 0) { dinva[k] = inva; dinvb[k] = invb; }
     TSYNC();
@@ -706,6 +712,18 @@ __device__ __forceinline__ LdlTab ldlTabStage(const DevModel& D, int* buf, Tm t)
   T.dlvl_start = put(D.dlvl_start, D.ndlevel + 1); T.dlvl_dofs = put(D.dlvl_dofs, nv); T.desc_start = put(D.desc_start, nv + 1);
   T.desc_dof = put(D.desc_dof, nd); T.desc_idx = put(D.desc_idx, nd); T.dof_Madr = put(D.dof_Madr, nv); T.dof_rowlen = put(D.dof_rowlen, nv);
   T.M_col = put(D.M_col, D.nM);
+  return T;
+}
+__host__ __device__ __forceinline__ int ldlFacTabInts(int nv, int nldlop) { return (nv + 1) + 3 * nldlop + 2 * nv; }
+__device__ __forceinline__ LdlFacTab ldlFacTabStage(const DevModel& D, int* buf, Tm t) {
+  const int nv = D.nv;
+  int* p = buf;
+  const unsigned live = __activemask();
+  const int nlive = __popc(live), rank = __popc(live & ((1u << (threadIdx.x & 31)) - 1u));
+  auto put = [&](const int* src, int n) { for (int i = t.tl * nlive + rank; i < n; i += t.nw * nlive) p[i] = src[i]; const int* r = p; p += n; return r; };
+  LdlFacTab T;
+  T.ldl_start = put(D.ldl_start, nv + 1); T.ldl_dst = put(D.ldl_dst, D.nldlop); T.ldl_a = put(D.ldl_a, D.nldlop); T.ldl_b = put(D.ldl_b, D.nldlop);
+  T.dof_Madr = put(D.dof_Madr, nv); T.dof_rowlen = put(D.dof_rowlen, nv);
   return T;
 }
 // x <- (L^T D L)^-1 x, by dof-tree levels
@@ -767,9 +785,10 @@ __device__ __noinline__ void inertia(int slot, int fslot, SP sm, Tm t, World W, 
   const float h = D.timestep;
   if (stage.p) {
     SP A = stage, B = stage + D.nM;
+    const LdlFacTab T = ldlFacTabStage(D, (int*)(stage.p - (threadIdx.x & 31) + 2 * D.nM * SCR), t);   // (the tables follow the lanes' block)
     TFOR(e, D.nM) { const float v = sm[L.qM + e]; A[e] = v; B[e] = v + (D.M_row[e] == D.M_col[e] ? h * D.dof_damping[D.M_row[e]] : 0.f); }
     TSYNC();
-    if (damp) factorLDL2(slot, A, sm + L.qLDinv, B, sm + L.qHinv, t); else factorLDL(slot, A, sm + L.qLDinv, t);
+    if (damp) factorLDL2(slot, A, sm + L.qLDinv, B, sm + L.qHinv, t, T); else factorLDL(slot, A, sm + L.qLDinv, t, T);
     TFOR(e, D.nM) { sm[L.qLD + e] = A[e]; if (damp) sm[L.qH + e] = B[e]; }
     TSYNC();
   } else {

@@ -13,7 +13,7 @@ void myo_make_layout(DevModel& D, int nconmax_req, int njmax_req, SmemLayout& L)
 
 #define MYO_PARAM_SLOTS 16   // live batches per process: one constant-memory parameter slot each (17 x ~2.3 KB of the 64 KB)
 // The kernels of the pipeline (tile.cu, lane = world): one entry per phase
-enum { MYO_K_KIN = 0, MYO_K_TENDON, MYO_K_INERTIA, MYO_K_COLLIDE, MYO_K_VELACT, MYO_K_FINISH, MYO_K_CONOUT, MYO_K_NEWTON, MYO_K_COLLIDE_MPR, MYO_K_COLLIDE_COMPACT, MYO_K_MAKECON, MYO_K_POSOUT, MYO_K_TENOUT };
+enum { MYO_K_KIN = 0, MYO_K_TENDON, MYO_K_INERTIA, MYO_K_COLLIDE, MYO_K_VELACT, MYO_K_FINISH, MYO_K_CONOUT, MYO_K_NEWTON, MYO_K_COLLIDE_MPR, MYO_K_COLLIDE_COMPACT, MYO_K_MAKECON, MYO_K_POSOUT, MYO_K_TENOUT, MYO_K_COMPACT_MAKECON };
 enum { MYO_KIN_LOAD = 1, MYO_KIN_RESET = 2, MYO_KIN_CHECK = 4 };                 // flags of MYO_K_KIN
 enum { MYO_FIN_EULER = 1, MYO_FIN_STATE = 2, MYO_FIN_WARM = 4, MYO_FIN_ACC = 8 };  // flags of MYO_K_FINISH
 int myo_tile_upload(int slot, const DevModel& D, const SmemLayout& L, const FieldPtrs& F, const TileAux& X, void* stream);

@@ -62,16 +62,23 @@ struct Timeline {
   }
   __device__ __forceinline__ ~Timeline() { if (p) atomicMax(p + 1, now()); }
 };
-__device__ __forceinline__ Ctx tileCtx(int slot, int nworld, const int* mask, float* scratch) {
+__device__ __forceinline__ Ctx tileCtxAt(int slot, int nworld, const int* mask, float* scratch, int tile) {
   Ctx c;
   const int lane = threadIdx.x & 31;
   c.t.tl = threadIdx.x >> 5; c.t.nw = blockDim.x >> 5;
-  const size_t w = (size_t)blockIdx.x * 32 + lane;
+  const size_t w = (size_t)tile * 32 + lane;
   c.live = w < (size_t)nworld && !(mask && !mask[w]);
   c.W.w = w; c.W.nw = (size_t)nworld;
-  c.sm.p = scratch + (size_t)blockIdx.x * tP[slot].L.total * SCR + lane;   // this tile's block, this lane's column
+  c.sm.p = scratch + (size_t)tile * tP[slot].L.total * SCR + lane;   // this tile's block, this lane's column
   return c;
 }
+__device__ __forceinline__ Ctx tileCtx(int slot, int nworld, const int* mask, float* scratch) { return tileCtxAt(slot, nworld, mask, scratch, blockIdx.x); }
+// Output kernels off the critical path (posout, tenout) run on a LIMITED grid, each CTA walking tiles blockIdx.x, + gridDim.x,
+// ...: a kernel of one CTA per tile holds its SM slots for its whole duration (all 256 tiles are resident at once), and stream
+// priorities only decide between CTAs that are still waiting -- so a full-grid output kernel made the solver's feeders
+// (collideCompact, makecon) wait tens of microseconds for slots.  The lanes of a partial last tile exit there: it is the last
+// tile of the CTA that gets it.  With a world mask any tile can have dead lanes: the host then launches one CTA per tile.
+#define TILE_LOOP(tile) for (int tile = blockIdx.x, ntiles_ = (nworld + 31) >> 5; tile < ntiles_; tile += gridDim.x)
 
 // ------------------------------------------------------------------------------------------ kin: state in, mj_kinematics, mj_comPos
 __global__ void __launch_bounds__(32 * MAXW, MINB_KIN) kinKernel(int slot, int fslot, int nworld, const int* __restrict__ mask, int flags,
@@ -128,9 +135,12 @@ __global__ void __launch_bounds__(32 * MAXW, MINB_KIN) kinKernel(int slot, int f
 #endif
 __global__ void __launch_bounds__(32 * MAXW, MINB_POSOUT) posoutKernel(int slot, int fslot, int nworld, const int* __restrict__ mask, float* __restrict__ scratch) {
   Timeline tline(slot, MYO_K_POSOUT);
-  Ctx c = tileCtx(slot, nworld, mask, scratch);
-  if (!c.live) return;
-  writePositionOutputs(slot, fslot, c.sm, c.t, c.W);
+  TILE_LOOP(tile) {
+    Ctx c = tileCtxAt(slot, nworld, mask, scratch, tile);
+    if (!c.live) return;
+    writePositionOutputs(slot, fslot, c.sm, c.t, c.W);
+    TSYNC();
+  }
 }
 
 // ------------------------------------------------------------------------------------------ tendon: mj_tendon (+ path points)
@@ -335,13 +345,8 @@ __global__ void __launch_bounds__(128) collideMprKernel(int slot, float* __restr
 }
 // collide B: in-order compaction of the hits into contact records -- contact order (hence geom1 / geom2 / efc_address) is
 // MuJoCo's
-__global__ void __launch_bounds__(32 * MAXW, 2) collideCompactKernel(int slot, int nworld, const int* __restrict__ mask, float* __restrict__ scratch) {
+__device__ __noinline__ void compactTile(int slot, SP sm, Tm t, unsigned lmask) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
-  Timeline tline(slot, MYO_K_COLLIDE_COMPACT);
-  Ctx c = tileCtx(slot, nworld, mask, scratch);
-  const unsigned lmask = __ballot_sync(0xffffffffu, c.live);
-  if (!c.live) return;
-  SP sm = c.sm; Tm t = c.t;
   const int lane = threadIdx.x & 31, nw = t.nw;
   __shared__ int sCnt[MAXW][32];
   if (D.npair == 0 || (D.disableflags & (DSBL_CONTACT | DSBL_CONSTRAINT))) return;
@@ -375,6 +380,13 @@ __global__ void __launch_bounds__(32 * MAXW, 2) collideCompactKernel(int slot, i
     }
     sm[L.counts] = __int_as_float(ncon);
   }
+}
+__global__ void __launch_bounds__(32 * MAXW, 2) collideCompactKernel(int slot, int nworld, const int* __restrict__ mask, float* __restrict__ scratch) {
+  Timeline tline(slot, MYO_K_COLLIDE_COMPACT);
+  Ctx c = tileCtx(slot, nworld, mask, scratch);
+  const unsigned lmask = __ballot_sync(0xffffffffu, c.live);
+  if (!c.live) return;
+  compactTile(slot, c.sm, c.t, lmask);
 }
 
 // ------------------------------------------------------------------------------------------ newton: mj_makeConstraint, mj_fwdConstraint
@@ -479,9 +491,12 @@ __device__ __noinline__ void tendonOutputs(int slot, int fslot, SP sm, Tm t, Wor
 #endif
 __global__ void __launch_bounds__(32 * MAXW, MINB_TENOUT) tenoutKernel(int slot, int fslot, int nworld, const int* __restrict__ mask, float* __restrict__ scratch) {
   Timeline tline(slot, MYO_K_TENOUT);
-  Ctx c = tileCtx(slot, nworld, mask, scratch);
-  if (!c.live) return;
-  tendonOutputs(slot, fslot, c.sm, c.t, c.W);
+  TILE_LOOP(tile) {
+    Ctx c = tileCtxAt(slot, nworld, mask, scratch, tile);
+    if (!c.live) return;
+    tendonOutputs(slot, fslot, c.sm, c.t, c.W);
+    TSYNC();
+  }
 }
 __device__ __noinline__ int tileMinI(Tm t, int v) {
   __shared__ int sc[MAXW][32];
@@ -1316,6 +1331,23 @@ __global__ void __launch_bounds__(32 * MAXW, MINB_MAKECON) makeconKernel(int slo
   const int nefc = makeConstraintTile(slot, sm, t, ncon, nconT, &status);
   if (t.tl == 0) { sm[L.counts + 1] = __int_as_float(nefc); sm[L.wstate + WS_STATUS] = __int_as_float(status); }
 }
+// collideCompact + makecon in one launch (models without tendon limits): both work on the tile's own records, and the kernel
+// boundary between them cost the solver's critical path ~40 us of waiting for SM slots.
+__global__ void __launch_bounds__(32 * MAXW, MINB_MAKECON) compactMakeconKernel(int slot, int nworld, const int* __restrict__ mask, float* __restrict__ scratch) {
+  const SmemLayout& L = tP[slot].L;
+  Timeline tline(slot, MYO_K_MAKECON);
+  Ctx c = tileCtx(slot, nworld, mask, scratch);
+  const unsigned lmask = __ballot_sync(0xffffffffu, c.live);
+  if (!c.live) return;
+  SP sm = c.sm; Tm t = c.t;
+  compactTile(slot, sm, t, lmask);
+  TSYNC();
+  int status = __float_as_int(sm[L.wstate + WS_STATUS]);
+  const int ncon = __float_as_int(sm[L.counts]);
+  const int nconT = __reduce_max_sync(lmask, ncon);
+  const int nefc = makeConstraintTile(slot, sm, t, ncon, nconT, &status);
+  if (t.tl == 0) { sm[L.counts + 1] = __int_as_float(nefc); sm[L.wstate + WS_STATUS] = __int_as_float(status); }
+}
 static inline size_t newtonSmemFloats(int nv) { return (size_t)(TRI(nv) + 7 * nv) * 32; }   // (+ the LDL solve's index tables, myo_tile_launch)
 #define NEWTON_SMEM_MAX (190 * 1024)   // + ~31 KB of static reduction / scan buffers <= 227 KB per CTA
 __global__ void __launch_bounds__(32 * MAXW, MINB_NEWTON) newtonKernel(int slot, int fslot, int nworld, const int* __restrict__ mask, int check_acc,
@@ -1435,14 +1467,15 @@ int myo_tile_launch(int kernel, int slot, int fslot, int nworld, const int* mask
   static const int nwKin = envInt("MYO_NW_KIN", 12), nwTen = envInt("MYO_NW_TEN", 12), nwIne = envInt("MYO_NW_INE", 12),
                    nwCol = envInt("MYO_NW_COL", 12), nwVel = envInt("MYO_NW_VEL", 12), nwFin = envInt("MYO_NW_FIN", 8),
                    nwOut = std::min(8, envInt("MYO_NW_OUT", 8)), yOut = envInt("MYO_Y_OUT", 4), nwNew = envInt("MYO_NW_NEWTON", 12),
-                   nwMak = envInt("MYO_NW_MAKECON", 12), nwPos = envInt("MYO_NW_POSOUT", 12);
+                   nwMak = envInt("MYO_NW_MAKECON", 12), nwPos = envInt("MYO_NW_POSOUT", 12), outGrid = std::max(1, envInt("MYO_OUT_GRID", 1 << 30));   // (limited grids measured: 148 CTAs +3 % step time, 74 +4 %, 48 +15 % -- the output kernels need the whole machine to finish inside the step)
   const int tiles = (nworld + 31) / 32;
   cudaStream_t st = (cudaStream_t)stream;
   switch (kernel) {
     case MYO_K_KIN: kinKernel<<<tiles, 32 * nwKin, 0, st>>>(slot, fslot, nworld, mask, flags, scratch); break;
     case MYO_K_TENDON: tendonKernel<<<tiles, 32 * nwTen, 0, st>>>(slot, fslot, nworld, mask, scratch); break;
-    case MYO_K_INERTIA: {   // flags: euler | nM << 8; shared memory: two copies of the factor's pattern per lane (<= 48 KB, else the scratch path)
-      const size_t sh = (size_t)2 * (flags >> 8) * 32 * sizeof(float);
+    case MYO_K_INERTIA: {   // flags: euler | nM << 8 | ints of the factorisation's index tables << 20; shared memory: two copies of
+      // the factor's pattern per lane + the tables (<= 48 KB, else the scratch path)
+      const size_t sh = (size_t)2 * ((flags >> 8) & 0xfff) * 32 * sizeof(float) + (size_t)(flags >> 20) * sizeof(int);
       const int staged = sh > 0 && sh <= 48 * 1024;
       inertiaKernel<<<tiles, 32 * nwIne, staged ? sh : 0, st>>>(slot, fslot, nworld, mask, flags & 1, staged, scratch);
     } break;
@@ -1471,8 +1504,9 @@ int myo_tile_launch(int kernel, int slot, int fslot, int nworld, const int* mask
       }
       newtonKernel<<<tiles, 32 * nwNew, shmem, st>>>(slot, fslot, nworld, mask, flags & 1, use_smem, (flags & 32) ? ((flags >> 1) & 15) : -1, scratch);
     } break;
-    case MYO_K_TENOUT: tenoutKernel<<<tiles, 32 * nwPos, 0, st>>>(slot, fslot, nworld, mask, scratch); break;
-    case MYO_K_POSOUT: posoutKernel<<<tiles, 32 * nwPos, 0, st>>>(slot, fslot, nworld, mask, scratch); break;
+    case MYO_K_TENOUT: tenoutKernel<<<mask ? tiles : std::min(tiles, outGrid), 32 * nwPos, 0, st>>>(slot, fslot, nworld, mask, scratch); break;
+    case MYO_K_POSOUT: posoutKernel<<<mask ? tiles : std::min(tiles, outGrid), 32 * nwPos, 0, st>>>(slot, fslot, nworld, mask, scratch); break;
+    case MYO_K_COMPACT_MAKECON: compactMakeconKernel<<<tiles, 32 * nwMak, 0, st>>>(slot, nworld, mask, scratch); break;
     case MYO_K_MAKECON: makeconKernel<<<tiles, 32 * nwMak, 0, st>>>(slot, nworld, mask, scratch); break;
     case MYO_K_CONOUT: conoutKernel<<<dim3(tiles, yOut), 32 * nwOut, 0, st>>>(slot, fslot, nworld, mask, scratch); break;
     default: return -1;
