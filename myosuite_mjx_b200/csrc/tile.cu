@@ -355,7 +355,13 @@ __device__ __noinline__ void compactTile(int slot, SP sm, Tm t, unsigned lmask) 
   const int ncand = __float_as_int(sm[L.counts + 3]);
   const int kc = (__reduce_max_sync(lmask, ncand) + nw - 1) / nw, k0 = min(ncand, t.tl * kc), k1 = min(ncand, k0 + kc);
   int cnt = 0;
-  for (int k = k0; k < k1; k++) cnt += __float_as_int(tmp[32 * k]) & 0xff;
+  for (int kb = k0; kb < k1; kb += 8) {   // (hit counts of eight survivors loaded together)
+    int h[8];
+#pragma unroll
+    for (int u = 0; u < 8; u++) h[u] = kb + u < k1 ? __float_as_int(tmp[32 * (kb + u)]) : 0;
+#pragma unroll
+    for (int u = 0; u < 8; u++) cnt += h[u] & 0xff;
+  }
   sCnt[t.tl][lane] = cnt;
   TSYNC();
   int at = 0, ncon = 0;
@@ -366,7 +372,11 @@ __device__ __noinline__ void compactTile(int slot, SP sm, Tm t, unsigned lmask) 
       if (at >= D.nconmax) continue;
       const int pr = cand[k];
       auto cr = sm + L.con + 12 * at; auto o = tmp + 32 * k + 1 + 7 * q;
-      for (int e = 0; e < 7; e++) cr[e] = o[e];
+      float rec[7];
+#pragma unroll
+      for (int e = 0; e < 7; e++) rec[e] = o[e];
+#pragma unroll
+      for (int e = 0; e < 7; e++) cr[e] = rec[e];
       cr[7] = __int_as_float(pr | (sw << 30)); cr[8] = __int_as_float(-1); cr[9] = __int_as_float(D.pair_dim[pr]);
       // dofs that move exactly one of the two bodies (static per pair): the only non-zero columns of the contact's rows
       const int f1 = D.cg_frame[D.pair_cg1[pr]], f2 = D.cg_frame[D.pair_cg2[pr]];
@@ -614,19 +624,36 @@ __device__ __noinline__ int makeConstraintTile(int slot, SP sm, Tm t, int ncon, 
       const unsigned f1lo = (unsigned)D.fr_mask[2 * f1], f1hi = (unsigned)D.fr_mask[2 * f1 + 1];
       const f3 pos = ld3(cr + 1), n = ld3(cr + 4);
       f3 y, z; makeFrame(n, &y, &z);
-      for (int k = 0; k < nv; k++) {
-        auto J = Jc + k;
-        const unsigned bit = 1u << (k & 31);
-        if (!((k < 32 ? mlo : mhi) & bit)) {   // dof k moves both bodies or neither
-          J[0] = 0.f; if (nb > 1) { J[nv] = 0.f; J[2 * nv] = 0.f; } if (nb > 3) J[3 * nv] = 0.f; continue;
+      // four dofs per iteration, their cdof / tree-centre loads issued together (one dof at a time was a chain of ~2 nv
+      // scratch latencies per contact: the bulk of this kernel)
+      for (int k0 = 0; k0 < nv; k0 += 4) {
+        float cdv[4][6], rc[4][3]; bool on[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+          const int k = k0 + u;
+          on[u] = k < nv && (((k < 32 ? mlo : mhi) >> (k & 31)) & 1u);   // off: dof k moves both bodies or neither
+          if (on[u]) {
+            auto cd = sm + L.cdof + 6 * k; auto rt = sm + L.rootcom + 3 * D.fr_root[D.dof_frame[k]];
+#pragma unroll
+            for (int e = 0; e < 6; e++) cdv[u][e] = cd[e];
+#pragma unroll
+            for (int e = 0; e < 3; e++) rc[u][e] = rt[e];
+          }
         }
-        const float sgn = ((k < 32 ? f1lo : f1hi) & bit) ? -1.f : 1.f;   // it moves exactly one of them: the first (-) or the second (+)
-        auto cd = sm + L.cdof + 6 * k;
-        const f3 jr = ld3(cd) * sgn;
-        const f3 jp = (ld3(cd + 3) + cross(ld3(cd), pos - ld3(sm + L.rootcom + 3 * D.fr_root[D.dof_frame[k]]))) * sgn;
-        J[0] = dot(n, jp);
-        if (nb > 1) { J[nv] = dot(y, jp); J[2 * nv] = dot(z, jp); }
-        if (nb > 3) J[3 * nv] = dot(n, jr);
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+          const int k = k0 + u;
+          if (k >= nv) break;
+          auto J = Jc + k;
+          if (!on[u]) { J[0] = 0.f; if (nb > 1) { J[nv] = 0.f; J[2 * nv] = 0.f; } if (nb > 3) J[3 * nv] = 0.f; continue; }
+          const float sgn = (((k < 32 ? f1lo : f1hi) >> (k & 31)) & 1u) ? -1.f : 1.f;   // it moves exactly one of them: the first (-) or the second (+)
+          const f3 w = mk3(cdv[u][0], cdv[u][1], cdv[u][2]);
+          const f3 jr = w * sgn;
+          const f3 jp = (mk3(cdv[u][3], cdv[u][4], cdv[u][5]) + cross(w, pos - mk3(rc[u][0], rc[u][1], rc[u][2]))) * sgn;
+          J[0] = dot(n, jp);
+          if (nb > 1) { J[nv] = dot(y, jp); J[2 * nv] = dot(z, jp); }
+          if (nb > 3) J[3 * nv] = dot(n, jr);
+        }
       }
     }
     TSYNC();
@@ -1316,7 +1343,7 @@ __global__ void __launch_bounds__(32 * MAXW, MINB_FINISH) finishKernel(int slot,
 // mj_makeConstraint as its own launch: it needs the contacts and the velocity, not the smooth forces, so it runs on the
 // collision stream beside the tendon / actuation stages (models with tendon limits: after them, api.cu).
 #ifndef MINB_MAKECON
-#define MINB_MAKECON 3
+#define MINB_MAKECON 2   // (80 registers: the batched Jacobian loads spill at 56; -0.5 % step time)
 #endif
 __global__ void __launch_bounds__(32 * MAXW, MINB_MAKECON) makeconKernel(int slot, int nworld, const int* __restrict__ mask, float* __restrict__ scratch) {
   const SmemLayout& L = tP[slot].L;
