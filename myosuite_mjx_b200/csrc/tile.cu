@@ -219,6 +219,33 @@ __device__ __forceinline__ bool isMprPair(const DevModel& D, const SmemLayout& L
   const int t1 = ovr ? __float_as_int(sm[L.cgshape + 5 * c1]) : D.cg_type[c1], t2 = ovr ? __float_as_int(sm[L.cgshape + 5 * c2]) : D.cg_type[c2];
   return t1 != G_PLANE && !((t1 == G_SPHERE || t1 == G_CAPSULE) && (t2 == G_SPHERE || t2 == G_CAPSULE) && !(t1 == G_CAPSULE && t2 == G_SPHERE));
 }
+// Support value h(d) = max over the shape of (x - centre) . d, for a unit direction d in world coordinates (float32).
+__device__ __forceinline__ float supportValue(int type, f3 size, SP R, f3 d) {
+  const f3 l = mk3(R[0] * d.x + R[3] * d.y + R[6] * d.z, R[1] * d.x + R[4] * d.y + R[7] * d.z, R[2] * d.x + R[5] * d.y + R[8] * d.z);   // R^T d
+  switch (type) {
+    case G_SPHERE: return size.x;
+    case G_CAPSULE: return size.x + size.y * fabsf(l.z);
+    case G_ELLIPSOID: return sqrtf(size.x * size.x * l.x * l.x + size.y * size.y * l.y * l.y + size.z * size.z * l.z * l.z);
+    case G_CYLINDER: return size.x * sqrtf(l.x * l.x + l.y * l.y) + size.y * fabsf(l.z);
+    case G_BOX: return size.x * fabsf(l.x) + size.y * fabsf(l.y) + size.z * fabsf(l.z);
+    default: return 3.4e38f;   // unknown to this test: never separated
+  }
+}
+// The portal search's first exit, in float32 and ahead of the work list: along the line of centres u the margin-inflated shapes
+// are apart when |c2 - c1| >= h1(u) + h2(-u) + margin (mprPenetration: dot(s1.v, dir) <= 0).  With a float32 safety band the
+// test is conservative: a pair it removes is one the float64 search would drop at its first step; the rest go on the list.
+__device__ __forceinline__ bool centreAxisApart(const DevModel& D, const SmemLayout& L, SP sm, bool ovr, int pr) {
+  const int c1 = D.pair_cg1[pr], c2 = D.pair_cg2[pr];
+  const CgShape S1 = cgShape(D, L, sm, ovr, c1), S2 = cgShape(D, L, sm, ovr, c2);
+  auto P1 = sm + L.cgpose + 12 * c1; auto P2 = sm + L.cgpose + 12 * c2;
+  const f3 v0 = ld3(P2) - ld3(P1);
+  const float dist = norm3(v0);
+  if (!(dist > 1e-6f)) return false;
+  const f3 u = v0 * (1.f / dist);
+  const float h1 = supportValue(S1.type, S1.size, P1 + 3, u), h2 = supportValue(S2.type, S2.size, P2 + 3, mk3(-u.x, -u.y, -u.z));
+  const float reach = h1 + h2 + D.pair_prm[16 * pr];
+  return dist > reach + 1e-5f * (dist + reach) + 1e-6f;
+}
 // collide A: geom poses, broad phase (ordered survivor list per lane), closed-form narrow phase.  Survivors that need the
 // convex narrow phase (MPR: float64, long, data-dependent) are appended to a batch-wide work list instead: a tile has a
 // handful of them per world at different survivor positions, so inside the tile they would run at a few active lanes
@@ -278,8 +305,9 @@ __global__ void __launch_bounds__(32 * MAXW, MINB_COLLIDE) collideKernel(int slo
   const int w = (int)c.W.w;
   for (int k = t.tl; k < ncand; k += nw) {
     const int pr = cand[k];
-    const bool mp = isMprPair(D, L, sm, ovr, pr);
-    if (!mp) {
+    bool mp = isMprPair(D, L, sm, ovr, pr);
+    if (mp && centreAxisApart(D, L, sm, ovr, pr)) { mp = false; tmp[32 * k] = __int_as_float(0); }   // no contact: not listed
+    else if (!mp) {
       Hit h[MAXHIT];
       int sw;
       const int n = collidePair<false>(slot, sm, pr, h, &sw);
