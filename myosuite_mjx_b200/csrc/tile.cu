@@ -360,11 +360,10 @@ __global__ void __launch_bounds__(128) collideMprKernel(int slot, float* __restr
     if (threadIdx.x == 0) sCount = 0;
     __syncthreads();
 #ifndef MPR_FILTER
-    // With the float32 centre-axis test in collideKernel four of five listed pairs do have a portal: the filter pass below only
-    // repeats their portal search (-0.9 % step time without it).  -DMPR_FILTER restores it.
+    // With the float32 centre-axis test in collideKernel four of five listed pairs do have a portal: a filter pass would only
+    // repeat their portal search (-0.9 % step time without it).  -DMPR_FILTER restores it.
     for (int k = threadIdx.x; k < batch && base + k < n; k += blockDim.x) record(base + k, false);
-    continue;
-#endif
+#else
     for (int k = threadIdx.x; k < batch && base + k < n; k += blockDim.x)
       if (!record(base + k, true)) sList[atomicAdd(&sCount, 1)] = base + k;
     __syncthreads();
@@ -375,6 +374,7 @@ __global__ void __launch_bounds__(128) collideMprKernel(int slot, float* __restr
     }
     for (int k = threadIdx.x; k < m; k += blockDim.x) record(sList[k], false);
     __syncthreads();
+#endif
   }
 }
 // collide B: in-order compaction of the hits into contact records -- contact order (hence geom1 / geom2 / efc_address) is
