@@ -340,8 +340,10 @@ __global__ void __launch_bounds__(128) collideMprKernel(int slot, float* __restr
   // two support evaluations, a few run tens of refinement steps.  One pair per lane straight through leaves ~5 of 32 lanes
   // busy (ncu: 5.25 threads per instruction); so the batch is filtered first, and the pairs that have a portal are
   // compacted in shared memory and run in full by consecutive lanes.  (Each record has its own slot: order is free.)
+#ifdef MPR_FILTER
   __shared__ int sList[MPR_BATCH];
   __shared__ int sCount;
+#endif
   auto record = [&](int i, bool filter) {
     const int2 e = X.mpr_list[i];
     SP sm; sm.p = scratch + (size_t)(e.x >> 5) * L.total * SCR + (e.x & 31);
@@ -357,8 +359,10 @@ __global__ void __launch_bounds__(128) collideMprKernel(int slot, float* __restr
   };
   const int batch = min(MPR_BATCH, max((int)blockDim.x, (int)(((n + gridDim.x - 1) / gridDim.x + blockDim.x - 1) / blockDim.x * blockDim.x)));
   for (int base = blockIdx.x * batch; base < n; base += gridDim.x * batch) {
+#ifdef MPR_FILTER
     if (threadIdx.x == 0) sCount = 0;
     __syncthreads();
+#endif
 #ifndef MPR_FILTER
     // With the float32 centre-axis test in collideKernel four of five listed pairs do have a portal: a filter pass would only
     // repeat their portal search (-0.9 % step time without it).  -DMPR_FILTER restores it.
