@@ -666,7 +666,11 @@ void myo_make_layout(DevModel& D, int nconmax_req, int njmax_req, SmemLayout& L)
   L.limrow = take(2 * (D.nlimj + D.nlimt));
   L.basev = take(2 * nb * D.nconmax);
   L.cand = take(D.npair); L.ctmp = take(32 * D.npair);   // survivor list and per-survivor narrow-phase records
+#ifdef KEEP_CONU
+  L.conU = take(nb * D.nconmax * nv);   // (debug: the old layout, region unused)
+#else
   L.conU = 0;   // (round-2 first builds kept U = W Jb here; syrkBlocks forms it in registers)
+#endif
   L.conW = take(8 * D.nconmax);         // per-contact weights of the active pyramid rows in base-row space
   int endB = o;
   L.total = std::max(endA, endB);

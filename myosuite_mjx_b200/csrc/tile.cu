@@ -754,7 +754,13 @@ template <int NB> __device__ __forceinline__ void syrkBlocks(int slot, SP sm, Tm
       for (int b = 0; b < NB; b++) {
         Wn[b] = Wi[b]; Wt[b] = b > 0 ? Wi[3 + b] : 0.f;   // Wn = (Wnn, Wnt[0..]), Wt = (-, Wtt[0..])
 #pragma unroll
-        for (int a = 0; a < 4; a++) { jr[b][a] = LDJ(Jr[(c * NB + b) * nv + a]); jc[b][a] = LDJ(Jc[(c * NB + b) * nv + a]); }
+        for (int a = 0; a < 4; a++) {
+#ifdef SYRK_CLAMP
+          jr[b][a] = 4 * R + a < nv ? LDJ(Jr[(c * NB + b) * nv + a]) : 0.f; jc[b][a] = 4 * C + a < nv ? LDJ(Jc[(c * NB + b) * nv + a]) : 0.f;
+#else
+          jr[b][a] = LDJ(Jr[(c * NB + b) * nv + a]); jc[b][a] = LDJ(Jc[(c * NB + b) * nv + a]);
+#endif
+        }
       }
 #pragma unroll
       for (int a = 0; a < 4; a++) {
@@ -924,7 +930,8 @@ __device__ __noinline__ void hessianUpdate(int slot, SP sm, Tm t, SP H, int nefc
 // Blocked left-looking Cholesky of H in place (L L^T = H), panels of CHB columns, two barriers per panel: (1) every row at
 // or below the panel takes the finished columns out of its panel entries (rows over warps); (2) every warp factors the
 // CHB x CHB diagonal block in registers -- redundantly, which saves the barrier a single owner would need -- and solves
-// its rows below against it.  The factor's diagonal goes to Hd (the solve divides by it).  All branches are warp-uniform.
+// its rows below against it; the factored block itself is written back after the panel's closing barrier (see there).
+// The factor's diagonal goes to Hd (the solve divides by it).  All branches are warp-uniform.
 #define CHB 6
 #define CHT(a, b) ((a) * ((a) + 1) / 2 + (b))
 __device__ __noinline__ void choleskyTile(int nv, SP H, SP Hd, Tm t) {
@@ -968,14 +975,6 @@ __device__ __noinline__ void choleskyTile(int nv, SP H, SP Hd, Tm t) {
         if (b < a) l[CHT(a, b)] = sacc * inv[b];
         else { const float d = sqrtf(fmaxf(sacc, MINVAL)); l[CHT(a, a)] = d; inv[a] = 1.f / d; }
       }
-    if (t.tl == 0) {
-#pragma unroll
-      for (int a = 0; a < CHB; a++) if (a < pb) {
-#pragma unroll
-        for (int b = 0; b < a; b++) H[TRI(j0 + a) + j0 + b] = l[CHT(a, b)];
-        Hd[j0 + a] = l[CHT(a, a)];
-      }
-    }
     for (int r = j0 + pb + t.tl; r < nv; r += nw) {
       auto Hr = H + TRI(r);
       float x[CHB];
@@ -990,7 +989,19 @@ __device__ __noinline__ void choleskyTile(int nv, SP H, SP Hd, Tm t) {
       for (int b = 0; b < CHB; b++) if (b < pb) Hr[j0 + b] = x[b];
     }
     TSYNC();
+    // The factored diagonal block goes back only now: every warp has read the unfactored block by the barrier above (writing
+    // it before that barrier raced with the slower warps' loads -- a whole tile's solve then ran on a half-factored block),
+    // and nothing reads these entries or Hd before cholSolveTile (the later panels' updates use the rows BELOW the blocks).
+    if (t.tl == 0) {
+#pragma unroll
+      for (int a = 0; a < CHB; a++) if (a < pb) {
+#pragma unroll
+        for (int b = 0; b < a; b++) H[TRI(j0 + a) + j0 + b] = l[CHT(a, b)];
+        Hd[j0 + a] = l[CHT(a, a)];
+      }
+    }
   }
+  TSYNC();
 }
 // x <- (L L^T)^-1 x with the factor above; y is a scratch vector.  Same panels, one barrier per panel each way: every warp
 // solves the panel's own unknowns redundantly, then takes them out of the rows it owns.
@@ -1154,7 +1165,12 @@ __device__ __noinline__ int newtonTile(int slot, SP sm, Tm t, const NewtonMem& M
     TICK(2);
     if (!__ballot_sync(lmask, active)) break;   // the tile is done when its slowest world is
     if (!active) { nefcA = 0; nconA = 0; }
-    if (pass == 0) { hessianAssemble(slot, sm, t, M.H, ncon, nconT, nefc); TICK(3); } else { hessianUpdate(slot, sm, t, M.H, nefcA, M.grad, M.Mv); TICK(4); }   // (grad, Mv: free between the gradient and the solve)
+#ifdef NO_HUPDATE
+    if (true) { hessianAssemble(slot, sm, t, M.H, ncon, nconT, nefc); TICK(3); } else {
+#else
+    if (pass == 0) { hessianAssemble(slot, sm, t, M.H, ncon, nconT, nefc); TICK(3); } else {
+#endif
+      hessianUpdate(slot, sm, t, M.H, nefcA, M.grad, M.Mv); TICK(4); }   // (grad, Mv: free between the gradient and the solve)
     choleskyTile(nv, M.H, M.Hd, t);
     TICK(5);
     pass++;

@@ -443,3 +443,27 @@ def test_quat_kat_on_device():
     np.testing.assert_allclose(prod.cpu().numpy(), k["mul"], rtol=1e-5, atol=1e-5)
     np.testing.assert_allclose(mat.cpu().numpy(), k["mat"], rtol=1e-5, atol=1e-5)
     np.testing.assert_allclose(rot.cpu().numpy(), k["rot"], rtol=1e-5, atol=1e-5)
+
+
+def test_rollout_is_bit_reproducible(models):
+    """Two batches stepped side by side from the same start stay bit-identical (8192 MyoHand worlds, 60 steps of the bench
+    rollout).  The step has no atomics in its arithmetic and every sum has a fixed order, so any difference is a race: this test
+    caught one (a warp wrote the factored diagonal block of the blocked Cholesky back while slower warps were still reading the
+    unfactored block; whole tiles then solved against a half-factored matrix, a few per thousand steps)."""
+    import torch
+    import bench
+    from myosuite_mjx_b200 import mjx, partition
+    m = models("hand")
+    model = mjx.put_model(m)
+    nw = 8192
+    q0 = bench.initial_qpos(m, nw, 1234)
+    A = mjx.put_data(model, dict(qpos=q0), nworld=nw, fields="all")
+    B = mjx.put_data(model, dict(qpos=q0), nworld=nw, fields="all")
+    for i in range(60):
+        if i % 10 == 0:
+            c = partition.ctrl_hash_torch(m.nu, 0, nw, 1234, i // 10, "cuda")
+            A.storage("ctrl").copy_(c); B.storage("ctrl").copy_(c)
+        mjx.step(model, A, 1); mjx.step(model, B, 1)
+    torch.cuda.synchronize()
+    for k in ("qpos", "qvel", "act", "qacc", "efc_force", "solver_niter", "contact_geom"):
+        assert torch.equal(getattr(A, k), getattr(B, k)), f"{k} differs between two identical rollouts"

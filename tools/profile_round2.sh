@@ -12,7 +12,7 @@ python bench.py --no-cpu --model legs > $out/${tag}_bench_legs.json 2>> $out/${t
 python bench.py --no-cpu --model hand_sar --steps 300 --no-steady > $out/${tag}_bench_hand_sar.json 2>> $out/${tag}_bench.err
 python bench.py --no-cpu --model finger --nworld 4096 > $out/${tag}_bench_finger4096.json 2>> $out/${tag}_bench.err
 python bench.py --no-cpu --model elbow --nworld 65536 --steps 300 > $out/${tag}_bench_elbow65536.json 2>> $out/${tag}_bench.err
-# launch list at steady state (13 launches per step incl. 4 empty ordering launches; the ctrl draw every 10 steps is torch's), the recipe's pass: cold caches, serialised
+# launch list at steady state (14 launches per step incl. 2 empty ordering launches; the ctrl draw every 10 steps is torch's), the recipe's pass: cold caches, serialised
 ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum,smsp__issue_active.avg.pct_of_peak_sustained_active,sm__warps_active.avg.per_cycle_active,smsp__thread_inst_executed_per_inst_executed.ratio,smsp__inst_executed.sum \
   --clock-control none --kernel-name regex:"Kernel" --launch-skip 4500 -c 60 --csv --log-file $out/${tag}_launches.csv python bench.py --no-cpu --no-steady --steps 40 --warmup 300 > $out/${tag}_ncu1.log 2>&1
 ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum \
