@@ -147,6 +147,11 @@ int myo_batch_create(const myo_model* m, int nworld, int nconmax, int njmax, myo
   try {
     myo_make_layout(b->D, nconmax, njmax, b->L);
   } catch (const std::string& e) { releaseSlot(b->slot); delete b; return fail(MYO_ERR_ARG, e); }
+  for (int f = 0; f < MYO_F_COUNT; f++)   // the kernels index fields with 32-bit element offsets k * nworld + w
+    if (fieldCount(b->D, f) * (int64_t)nworld >= ((int64_t)1 << 32)) {
+      releaseSlot(b->slot); delete b;
+      return fail(MYO_ERR_ARG, std::string("batch too large: field ") + kFieldNames[f] + " would exceed 2^32 elements (split the worlds over more batches)");
+    }
   {
     void* p = nullptr;
     // tile-blocked scratch [tiles][L.total][32]; zeroed once: a record the kernels have not written yet (rows past an

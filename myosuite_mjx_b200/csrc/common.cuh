@@ -170,15 +170,17 @@ struct Tm { int tl, nw; };
 #define FR_MAT(sm, L, f) ((sm) + (L).frames + 16 * (f) + 7)
 
 // batched field access, struct-of-arrays, world fastest: element k of world w lives at base[k * nworld + w]
-struct World { size_t w, nw; };
+struct World { size_t w, nw; unsigned w32, nw32; };   // (32-bit copies: field indices k * nworld + w fit 32 bits, myo_batch_create checks)
 // Element k of a [k][nworld] field for this lane's world.  Stores are streaming (st.global.cs, evict-first): the 640 MB of
 // output fields a step writes are never read back by it, and at plain priority they push the solver's working set (the
 // tiles' Jacobian blocks, ~100 MB at 8192 worlds, about the size of the L2) out to DRAM.  Reads (input fields) are plain.
 #ifndef NO_STREAM_OUT
 struct FRef { float* p; __device__ __forceinline__ void operator=(float v) const { __stcs(p, v); } __device__ __forceinline__ operator float() const { return *p; } };
 struct IRef { int* p; __device__ __forceinline__ void operator=(int v) const { __stcs(p, v); } __device__ __forceinline__ operator int() const { return *p; } };
-#define OUTF(ptr, k) (FRef{(float*)(ptr) + ((size_t)(k) * W.nw + W.w)})
-#define OUTI(ptr, k) (IRef{(int*)(ptr) + ((size_t)(k) * W.nw + W.w)})
+// (the element index in unsigned 32-bit arithmetic: one IMAD instead of the 64-bit multiply's four or five instructions per
+// access -- the output kernels are issue-bound on exactly this address arithmetic)
+#define OUTF(ptr, k) (FRef{(float*)(ptr) + ((unsigned)(k) * W.nw32 + W.w32)})
+#define OUTI(ptr, k) (IRef{(int*)(ptr) + ((unsigned)(k) * W.nw32 + W.w32)})
 #else
 #define OUTF(ptr, k) ((float*)(ptr))[(size_t)(k) * W.nw + W.w]
 #define OUTI(ptr, k) ((int*)(ptr))[(size_t)(k) * W.nw + W.w]

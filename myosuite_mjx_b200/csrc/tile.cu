@@ -68,7 +68,7 @@ __device__ __forceinline__ Ctx tileCtxAt(int slot, int nworld, const int* mask, 
   c.t.tl = threadIdx.x >> 5; c.t.nw = blockDim.x >> 5;
   const size_t w = (size_t)tile * 32 + lane;
   c.live = w < (size_t)nworld && !(mask && !mask[w]);
-  c.W.w = w; c.W.nw = (size_t)nworld;
+  c.W.w = w; c.W.nw = (size_t)nworld; c.W.w32 = (unsigned)w; c.W.nw32 = (unsigned)nworld;
   c.sm.p = scratch + (size_t)tile * tP[slot].L.total * SCR + lane;   // this tile's block, this lane's column
   return c;
 }
