@@ -76,6 +76,7 @@ struct DevModel {
   const float *ent_scale;                      // +-1/divisor
   const int *nz_estart, *nz_tendon, *nz_dof;   // [nnz+1], [nnz], [nnz]
   const int *ten_nzstart;                      // [nten+1]
+  const int *ten_dense, *act_dense;            // [nten][nv], [nu][nv]: source of each dense ten_J / actuator_moment entry (sparse index, -1 zero, -2 gear)
   const int *col_start, *col_nz;               // [nv+1], [nnz]  column view of the pattern
   const float *ten_range, *ten_stiffness, *ten_damping, *ten_lengthspring;
   // ---- actuators

@@ -429,6 +429,16 @@ void myo_build_plan(const myo_model_desc& m, int nconmax_req, int njmax_req, Dev
     for (int i = 0; i < nu; i++) { same[i] = 1; for (int k = 0; k < 9; k++) if (gp[9 * i + k] != bp[9 * i + k]) same[i] = 0; }
     D.act_same_prm = upload(same, owned);
     D.act_trntype = upload(tt, owned); D.act_trnid = upload(ti, owned); D.act_dyntype = upload(dt, owned); D.act_gaintype = upload(gt, owned);
+    {   // dense-row source maps of the tendon output kernel: entry (row, dof) -> index of the sparse moment-arm entry, -1 = zero,
+        // -2 = the gear itself (joint transmission): ten_J [nten][nv], actuator_moment [nu][nv]
+      std::vector<int> td((size_t)m.ntendon * nv, -1), ad((size_t)nu * nv, -1);
+      for (int t = 0; t < m.ntendon; t++) for (int n = ten_nzstart[t]; n < ten_nzstart[t + 1]; n++) td[(size_t)t * nv + nz_d[n]] = n;
+      for (int i = 0; i < nu; i++) {
+        if (tt[i] == 3) { const int t = ti[i]; for (int n = ten_nzstart[t]; n < ten_nzstart[t + 1]; n++) ad[(size_t)i * nv + nz_d[n]] = n; }
+        else ad[(size_t)i * nv + m.jnt_dofadr[ti[i]]] = -2;
+      }
+      D.ten_dense = upload(td, owned); D.act_dense = upload(ad, owned);
+    }
     D.act_biastype = upload(bt, owned); D.act_flags = upload(fl, owned); D.act_actadr = upload(aa, owned); D.act_gear = upload(gear, owned);
     D.act_dynprm = upload(dp, owned); D.act_gainprm = upload(gp, owned); D.act_biasprm = upload(bp, owned); D.act_ctrlrange = upload(cr, owned);
     std::vector<int> tas(m.ntendon + 1, 0), tal, das(nv + 1, 0), dal;

@@ -502,38 +502,36 @@ __device__ __noinline__ void tendonOutputs(int slot, int fslot, SP sm, Tm t, Wor
   }
   void* tl = F.p[MYO_F_TEN_LENGTH]; void* tj = F.p[MYO_F_TEN_J];
   if (tl) TFOR(k, D.nten) OUTF(tl, k) = sm[L.tenlen + k];
+  // dense ten_J and actuator_moment rows from the compile-time source map of every entry (plan.cu: sparse index, -1 zero,
+  // -2 the gear): independent items, four per iteration -- the serial merge of a sparse row into a dense one put a table
+  // lookup and a branch on every element's chain
+  const int nv = D.nv;
   if (tj) {
-    TFOR(k, D.nten) {   // dense row = zeros with the sparse entries (sorted by dof) merged in
-      int q = D.ten_nzstart[k];
-      const int qend = D.ten_nzstart[k + 1];
-      for (int i = 0; i < D.nv; i++) {
-        float v = 0.f;
-        if (q < qend && D.nz_dof[q] == i) { v = sm[L.tenJ + q]; q++; }
-        OUTF(tj, k * D.nv + i) = v;
-      }
+    const int n = D.nten * nv;
+    for (int i0 = t.tl; i0 < n; i0 += 4 * TEAM) {
+      float v[4];
+#pragma unroll
+      for (int u = 0; u < 4; u++) { const int i = i0 + u * TEAM; const int src = i < n ? D.ten_dense[i] : -1; v[u] = src >= 0 ? sm[L.tenJ + src] : 0.f; }
+#pragma unroll
+      for (int u = 0; u < 4; u++) if (i0 + u * TEAM < n) OUTF(tj, i0 + u * TEAM) = v[u];
     }
   }
-  // actuator_moment (mj_transmission): needs the tendon rows and the model only
-  const int nu = D.nu, nv = D.nv;
-  void* o;
-  if ((o = F.p[MYO_F_ACTUATOR_MOMENT])) {
-    TFOR(a, nu) {   // dense row = the tendon's sparse row scaled by the gear
-      const int id = D.act_trnid[a];
-      const bool ten = D.act_trntype[a] == 3;
-      int k = ten ? D.ten_nzstart[id] : 0;
-      const int kend = ten ? D.ten_nzstart[id + 1] : 0;
-      const int jd = ten ? -1 : D.jnt_dofadr[id];
-      const float gear = D.act_gear[a];
-      for (int i = 0; i < nv; i++) {
-        float v = 0.f;
-        if (k < kend && D.nz_dof[k] == i) { v = gear * sm[L.tenJ + k]; k++; }
-        if (i == jd) v = gear;
-        OUTF(o, a * nv + i) = v;
+  void* am = F.p[MYO_F_ACTUATOR_MOMENT];
+  if (am) {   // mj_transmission: needs the tendon rows and the model only
+    const int n = D.nu * nv;
+    for (int i0 = t.tl; i0 < n; i0 += 4 * TEAM) {
+      float v[4];
+#pragma unroll
+      for (int u = 0; u < 4; u++) {
+        const int i = i0 + u * TEAM; const int src = i < n ? D.act_dense[i] : -1;
+        const float gear = src != -1 ? D.act_gear[i / nv] : 0.f;
+        v[u] = src >= 0 ? gear * sm[L.tenJ + src] : gear;   // (-2: the gear itself; -1: gear = 0)
       }
+#pragma unroll
+      for (int u = 0; u < 4; u++) if (i0 + u * TEAM < n) OUTF(am, i0 + u * TEAM) = v[u];
     }
   }
 }
-
 #ifndef MINB_TENOUT
 #define MINB_TENOUT 3
 #endif
