@@ -1144,6 +1144,7 @@ __device__ __noinline__ int newtonTile(int slot, SP sm, Tm t, const NewtonMem& M
   // per-contact loop of the later passes (their trip counts are per lane), so a pass that only serves the tile's stragglers
   // runs to THEIR row counts and loads only their lines.
   int nefcA = nefc, nconA = ncon;
+  bool forceOut = nefc == 0;   // (a world without rows: the caller zeroes its qfrc_constraint)
   const int lsmax = D.ls_iterations;
   for (;;) {
     // gradient and termination tests
@@ -1161,6 +1162,10 @@ __device__ __noinline__ int newtonTile(int slot, SP sm, Tm t, const NewtonMem& M
     if (active && iter > 0 && (scale * gn < D.tolerance || gn < GRAD_NOISE * gr)) active = false;
     if (active && iter >= D.iterations) { *status |= MYO_WORLD_SOLVER_MAXITER; active = false; }
     TICK(2);
+    // A world that has just stopped iterating (here, or at the end of the last pass) has its final J^T f in tmp -- this pass's
+    // force evaluation still covered it -- and its final efc_force in the rows: qfrc_constraint goes out now, and no force
+    // evaluation is needed after the loop (the loop only exits here, right after one).
+    if (!active && !forceOut) { TFOR(k, nv) sm[L.qfrc_con + k] = tmp[k]; forceOut = true; }
     if (!__ballot_sync(lmask, active)) break;   // the tile is done when its slowest world is
     if (!active) { nefcA = 0; nconA = 0; }
 #ifdef NO_HUPDATE
@@ -1280,7 +1285,6 @@ __device__ __noinline__ int newtonTile(int slot, SP sm, Tm t, const NewtonMem& M
     }
     TICK(9);
   }
-  constraintForce(slot, sm, t, ncon, nefc, sm + L.qfrc_con);
   TICK(10);
   return iter;
 }
