@@ -1514,7 +1514,10 @@ __device__ __noinline__ float residualCost(int slot, SP sm, Tm t, int ncon, int 
   TFOR(r, nefc) {
     const float jar = rowMul(slot, sm, r, x, bx) - EFC(E_AREF, r);
     EFC(E_JAR, r) = jar;
-    if (rowOn(EFCI(E_DESC0, r), jar)) cost = fmaf(0.5f * EFC(E_D, r) * jar, jar, cost);
+    const bool on = rowOn(EFCI(E_DESC0, r), jar);
+    const float Dr = EFC(E_D, r);
+    EFC(E_FORCE, r) = on ? -Dr * jar : 0.f;   // (every writer of E_JAR leaves the row's force beside it: constraintForce reads it)
+    if (on) cost = fmaf(0.5f * Dr * jar, jar, cost);
   }
   TSYNC();
   return TSUM(cost);
@@ -1542,8 +1545,10 @@ __device__ __noinline__ void residualCost2(int slot, SP sm, Tm t, int ncon, int 
       if (r < nefc) {
         const float jar0 = j0[u] - aref[u], jar1 = j1[u] - aref[u];
         EFC(E_JAR, r) = jar1;
+        const bool on1 = rowOn(d0[u], jar1);
+        EFC(E_FORCE, r) = on1 ? -Dr[u] * jar1 : 0.f;
         if (rowOn(d0[u], jar0)) c[0] = fmaf(0.5f * Dr[u] * jar0, jar0, c[0]);
-        if (rowOn(d0[u], jar1)) c[1] = fmaf(0.5f * Dr[u] * jar1, jar1, c[1]);
+        if (on1) c[1] = fmaf(0.5f * Dr[u] * jar1, jar1, c[1]);
       }
     }
   }
@@ -1608,7 +1613,7 @@ template <int G> __device__ __forceinline__ void jtForce(int slot, SP sm, Tm t, 
     for (int g = 0; g < G; g++) if (kb + g * TEAM < nv) out[kb + g * TEAM] = res[g] + a[g][0] + a[g][1];
   }
 }
-// forces from jar, then out = J^T f  (deterministic gathers, no atomics)
+// out = J^T f from the rows' forces  (deterministic gathers, no atomics)
 __device__ __noinline__ void constraintForce(int slot, SP sm, Tm t, int ncon, int nefc, SP out) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
   const int nv = D.nv, nb = D.maxbase;
@@ -1618,17 +1623,8 @@ __device__ __noinline__ void constraintForce(int slot, SP sm, Tm t, int ncon, in
 #else
 #define CFT(k)
 #endif
-  for (int rb = t.tl; rb < nefc; rb += RB * TEAM) {
-    float jar[RB], Dr[RB]; int d0[RB];
-#pragma unroll
-    for (int u = 0; u < RB; u++) {
-      const int r = rb + u * TEAM; const bool ok = r < nefc;
-      jar[u] = ok ? EFC(E_JAR, r) : 0.f; Dr[u] = ok ? EFC(E_D, r) : 0.f; d0[u] = ok ? EFCI(E_DESC0, r) : ROW_CON;
-    }
-#pragma unroll
-    for (int u = 0; u < RB; u++) { const int r = rb + u * TEAM; if (r < nefc) EFC(E_FORCE, r) = rowOn(d0[u], jar[u]) ? -Dr[u] * jar[u] : 0.f; }
-  }
-  TSYNC();
+  // (the rows' forces are already in E_FORCE: residualCost / residualCost2 and the solver's row update write them with E_JAR,
+  // behind barriers of their own)
   CFT(16);
   auto bf = sm + L.basev + nb * D.nconmax;
   // base-row forces of a contact from its pyramid rows (mju_decodePyramid, transposed); two contacts per iteration, their

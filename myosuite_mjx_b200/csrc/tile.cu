@@ -1268,7 +1268,9 @@ __device__ __noinline__ int newtonTile(int slot, SP sm, Tm t, const NewtonMem& M
             flip = (jar < 0.f ? 1.f : 0.f) - (old < 0.f ? 1.f : 0.f);   // the row joins (+1) or leaves (-1) the active set: hessianUpdate
           }
           EFC(E_JV, r) = flip;
-          if (rowOn(d0v[u], jar)) gc[1] = fmaf(0.5f * Drv[u] * jar, jar, gc[1]);
+          const bool on = rowOn(d0v[u], jar);
+          EFC(E_FORCE, r) = on ? -Drv[u] * jar : 0.f;   // (the flip list of hessianUpdate borrowed these entries; the next force evaluation reads them)
+          if (on) gc[1] = fmaf(0.5f * Drv[u] * jar, jar, gc[1]);
         }
       }
     }
