@@ -5,7 +5,7 @@ sys.path.insert(0, ROOT)
 import numpy as np, torch
 import bench
 from myosuite_mjx_b200 import mjx, partition
-m = bench.load_model("hand")
+m = bench.load_model(os.environ.get("MODEL", "hand"))
 model = mjx.put_model(m)
 nw, nsteps = 8192, int(sys.argv[1]) if len(sys.argv) > 1 else 300
 A = mjx.put_data(model, dict(qpos=bench.initial_qpos(m, nw, 1234)), nworld=nw, fields="all")
