@@ -361,7 +361,7 @@ static int launchPhases(myo_batch* b, int nsub, int forward_only, const int32_t*
       }
       const int fin = (forward_only ? 0 : MYO_FIN_EULER) | (last && (!forward_only || do_reset) ? MYO_FIN_STATE : 0) | (last ? MYO_FIN_WARM | MYO_FIN_ACC : 0);
       static const bool fuse_finish = !(getenv("MYO_FUSE_FINISH") && atoi(getenv("MYO_FUSE_FINISH")) == 0);   // developer knob
-      ok &= tile(MYO_K_NEWTON, fslot, (forward_only ? 0 : 1) | (fuse_finish ? (fin << 1) | 32 : 0) | (b->D.nv << 8) | (ldlTabIntsHost(b->D) << 16)) == 0;
+      ok &= tile(MYO_K_NEWTON, fslot, (forward_only ? 0 : 1) | (fuse_finish ? (fin << 1) | 32 : 0) | (b->D.nv << 8)) == 0;
       if (conout && conout_late) {
         ok &= cudaEventRecord(E(3), main) == cudaSuccess && cudaStreamWaitEvent(S(3), E(3), 0) == cudaSuccess;
         cur = b->side[3]; ok &= tile(MYO_K_CONOUT, fslot, 0) == 0; cur = stream;
@@ -388,7 +388,7 @@ static int launchPhases(myo_batch* b, int nsub, int forward_only, const int32_t*
     if (posvel) break;
     ok &= tile(MYO_K_MAKECON, fslot, 0) == 0; STOP_HERE();
     if (conout) { ok &= tile(MYO_K_CONOUT, fslot, 0) == 0; STOP_HERE(); }
-    ok &= tile(MYO_K_NEWTON, fslot, (forward_only ? 0 : 1) | (b->D.nv << 8) | (ldlTabIntsHost(b->D) << 16)) == 0; STOP_HERE();
+    ok &= tile(MYO_K_NEWTON, fslot, (forward_only ? 0 : 1) | (b->D.nv << 8)) == 0; STOP_HERE();
     ok &= tile(MYO_K_FINISH, fslot, (forward_only ? 0 : MYO_FIN_EULER) | (last && (!forward_only || do_reset) ? MYO_FIN_STATE : 0) |
                                         (last ? MYO_FIN_WARM | MYO_FIN_ACC : 0)) == 0;
   }

@@ -444,11 +444,18 @@ __global__ void __launch_bounds__(32 * MAXW, 2) collideCompactKernel(int slot, i
 // identical in every warp of the tile).  A world that has converged is masked out and the tile iterates until its slowest
 // world is done.  Per-lane scalars (cost, step size, iteration count, flags) are replicated in every warp: they come from
 // sums that are bit-identical in all warps, so all warps take the same branches.
+// One shared buffer for every tile-wide scan / minimum / sum (each use is bracketed by its own pair of barriers).  Small on
+// purpose: with 4 sums per call the solver kernel's two CTAs fit the 132 KB shared-memory configuration and L1 keeps 124 KB
+// instead of 92 (12 sums per call: 18 KB more per CTA).
+#ifndef MAXSUM
+#define MAXSUM 4
+#endif
+__device__ __forceinline__ float* tileRedBuf() { __shared__ float red[MAXSUM * MAXW * 32]; return red; }
 struct TileScan { int off, total; };
 // exclusive prefix of a per-(warp, lane) count over the warps of the tile, in warp order: warp j owns a contiguous chunk
 // of an item range, so per-lane ordered compaction needs no serial walk
 __device__ __noinline__ TileScan tileScan(Tm t, int cnt) {
-  __shared__ int sc[MAXW][32];
+  int (*sc)[32] = (int (*)[32])tileRedBuf();
   const int lane = threadIdx.x & 31;
   sc[t.tl][lane] = cnt;
   __syncthreads();
@@ -545,7 +552,7 @@ __global__ void __launch_bounds__(32 * MAXW, MINB_TENOUT) tenoutKernel(int slot,
   }
 }
 __device__ __noinline__ int tileMinI(Tm t, int v) {
-  __shared__ int sc[MAXW][32];
+  int (*sc)[32] = (int (*)[32])tileRedBuf();
   const int lane = threadIdx.x & 31;
   sc[t.tl][lane] = v;
   __syncthreads();
@@ -554,10 +561,9 @@ __device__ __noinline__ int tileMinI(Tm t, int v) {
   __syncthreads();
   return m;
 }
-// N sums at once (one pair of barriers)
-#define MAXSUM 12
-__device__ __forceinline__ float* tileRedBuf() { __shared__ float red[MAXSUM * MAXW * 32]; return red; }   // one buffer for every N
+// N <= MAXSUM sums at once (one pair of barriers)
 template <int N> __device__ __forceinline__ void tileSumN(Tm t, float* v) {
+  static_assert(N <= MAXSUM, "tileSumN: raise MAXSUM");
   float* red = tileRedBuf() + (threadIdx.x & 31);
 #pragma unroll
   for (int k = 0; k < N; k++) red[(k * MAXW + t.tl) * 32] = v[k];
@@ -1090,7 +1096,8 @@ template <int K> __device__ __forceinline__ void lsEvalTile(int slot, SP sm, Tm 
       }
     }
   }
-  tileSumN<4 * K>(t, q);
+#pragma unroll
+  for (int k = 0; k < K; k++) tileSumN<4>(t, q + 4 * k);   // (K = 3 only in the bracket refinement, a few percent of the evaluations)
 #pragma unroll
   for (int k = 0; k < K; k++) {
     const float q0 = q[4 * k] + qg[0], q1 = q[4 * k + 1] + qg[1], q2 = q[4 * k + 2] + qg[2], qa = q[4 * k + 3] + fabsf(qg[1]);
