@@ -170,6 +170,7 @@ def main():
     ap.add_argument("--nsub", type=int, default=1, help="mj_steps fused per launch")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-steady", action="store_true", help="skip the steady_state leg")
+    ap.add_argument("--count-aware", action="store_true", help="opt-in myo_batch_set_count_aware: contact_* / efc_* written up to ncon / nefc only (NOT the headline configuration)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local = int(os.environ.get("LOCAL_RANK", "0"))
     if args.impl == "reference":
@@ -191,6 +192,8 @@ def main():
     # worlds are partitioned by index: rank r owns [r*nw, (r+1)*nw); start states and controls are functions of the global index
     w0 = rank * nw
     d = mjx.put_data(model, dict(qpos=initial_qpos(m, nw, SEED, w0)), nworld=nw, fields=args.fields)
+    if args.count_aware:
+        d.set_count_aware(True)
     ctrl_buf = d.storage("ctrl")
     stream = torch.cuda.current_stream()
     step_no = [0]
@@ -321,7 +324,8 @@ def main():
     line = {"metric": "env-steps/s", "value": value, "unit": "env-steps/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic", "parity": PARITY,
-            "config": {"workload": WORKLOAD.format(model=args.model, nworld=nw), "nworld_per_gpu": nw, "fields": args.fields,
+            "config": {"workload": WORKLOAD.format(model=args.model, nworld=nw) + (" (count-aware: contact / constraint records up to ncon / nefc only)" if args.count_aware else ""),
+                       "nworld_per_gpu": nw, "fields": args.fields, "count_aware": bool(args.count_aware),
                        "nsub_per_launch": args.nsub, "frame_skip_ctrl_hold": FRAME_SKIP, "nconmax": d.nconmax, "njmax": d.njmax,
                        "scratch_bytes_per_world": d.smem_bytes, "engine": "phase pipeline, lane = world (32 worlds per tile CTA)",
                        "bytes_per_world_step": bytes_per_world, "live_bytes_per_world_step": int(live_bytes),

@@ -240,6 +240,12 @@ int myo_forward_posvel(myo_batch *b, const int32_t *world_mask_dev, void *cuda_s
  * Output fields describe the last substep's forward pass, as mjData does after mj_step. */
 int myo_step(myo_batch *b, int nsubsteps, void *cuda_stream);
 
+/* Count-aware outputs (opt-in, off by default).  MJX and this library pad contact_* and efc_* to nconmax / njmax and rewrite the
+ * padding (zeros; efc_type / contact_geom / contact_efc_address: -1) on every step, which is 60 % of those fields' bytes in
+ * the MyoHand rollout.  A caller that reads them only up to ncon / nefc -- as mjData consumers do -- can switch the padding
+ * off: with on != 0 the records of the contacts / rows that exist are written and the rest of the buffers is left alone. */
+int myo_batch_set_count_aware(myo_batch *b, int on);
+
 /* Kept for ABI stability with round 1 (whose separate wide-output kernel could be pipelined under the next step): every
  * field is now written, as full lines, by the pipeline phase that produces it, and is complete in stream order when
  * myo_step returns (mjx.step semantics).  Both calls are accepted and do nothing. */

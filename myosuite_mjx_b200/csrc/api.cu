@@ -330,7 +330,7 @@ static int launchPhases(myo_batch* b, int nsub, int forward_only, const int32_t*
         ok &= tile(fuse_rows ? MYO_K_COMPACT_MAKECON : MYO_K_MAKECON, fslot, 0) == 0;
         if (conout && !conout_late) {
           ok &= cudaEventRecord(E(3), on) == cudaSuccess && cudaStreamWaitEvent(S(3), E(3), 0) == cudaSuccess;
-          void* keep = cur; cur = b->side[3]; ok &= tile(MYO_K_CONOUT, fslot, 0) == 0; cur = keep;
+          void* keep = cur; cur = b->side[3]; ok &= tile(MYO_K_CONOUT, fslot, b->count_aware ? 1 : 0) == 0; cur = keep;
         }
       };
       // the position outputs start behind the broad phase: the convex narrow phase (201 registers per thread) then takes the
@@ -359,12 +359,12 @@ static int launchPhases(myo_batch* b, int nsub, int forward_only, const int32_t*
       if (posout && out_late) {
         ok &= cudaEventRecord(E(8), main) == cudaSuccess && cudaStreamWaitEvent((cudaStream_t)b->side[4], E(8), 0) == cudaSuccess;
       }
-      const int fin = (forward_only ? 0 : MYO_FIN_EULER) | (last && (!forward_only || do_reset) ? MYO_FIN_STATE : 0) | (last ? MYO_FIN_WARM | MYO_FIN_ACC : 0);
+      const int fin = (forward_only ? 0 : MYO_FIN_EULER) | (last && (!forward_only || do_reset) ? MYO_FIN_STATE : 0) | (last ? MYO_FIN_WARM | MYO_FIN_ACC | (b->count_aware ? MYO_FIN_LIVE : 0) : 0);
       static const bool fuse_finish = !(getenv("MYO_FUSE_FINISH") && atoi(getenv("MYO_FUSE_FINISH")) == 0);   // developer knob
-      ok &= tile(MYO_K_NEWTON, fslot, (forward_only ? 0 : 1) | (fuse_finish ? (fin << 1) | 32 : 0) | (b->D.nv << 8)) == 0;
+      ok &= tile(MYO_K_NEWTON, fslot, (forward_only ? 0 : 1) | (fuse_finish ? (fin << 1) | 32 : 0) | (b->count_aware ? 64 : 0) | (b->D.nv << 8)) == 0;
       if (conout && conout_late) {
         ok &= cudaEventRecord(E(3), main) == cudaSuccess && cudaStreamWaitEvent(S(3), E(3), 0) == cudaSuccess;
-        cur = b->side[3]; ok &= tile(MYO_K_CONOUT, fslot, 0) == 0; cur = stream;
+        cur = b->side[3]; ok &= tile(MYO_K_CONOUT, fslot, b->count_aware ? 1 : 0) == 0; cur = stream;
       }
       if (!fuse_finish) ok &= tile(MYO_K_FINISH, fslot, fin) == 0;
       if (posout && out_late) {
@@ -387,10 +387,10 @@ static int launchPhases(myo_batch* b, int nsub, int forward_only, const int32_t*
     ok &= tile(MYO_K_VELACT, fslot, (posvel ? 1 : 0) | (velactStage(b->D))) == 0; STOP_HERE();
     if (posvel) break;
     ok &= tile(MYO_K_MAKECON, fslot, 0) == 0; STOP_HERE();
-    if (conout) { ok &= tile(MYO_K_CONOUT, fslot, 0) == 0; STOP_HERE(); }
+    if (conout) { ok &= tile(MYO_K_CONOUT, fslot, b->count_aware ? 1 : 0) == 0; STOP_HERE(); }
     ok &= tile(MYO_K_NEWTON, fslot, (forward_only ? 0 : 1) | (b->D.nv << 8)) == 0; STOP_HERE();
     ok &= tile(MYO_K_FINISH, fslot, (forward_only ? 0 : MYO_FIN_EULER) | (last && (!forward_only || do_reset) ? MYO_FIN_STATE : 0) |
-                                        (last ? MYO_FIN_WARM | MYO_FIN_ACC : 0)) == 0;
+                                        (last ? MYO_FIN_WARM | MYO_FIN_ACC | (b->count_aware ? MYO_FIN_LIVE : 0) : 0)) == 0;
   }
   if (!ok) return fail(MYO_ERR_CUDA, std::string("kernel launch failed: ") + cudaGetErrorString(cudaGetLastError()));
   return MYO_OK;
@@ -403,6 +403,11 @@ static int launch(myo_batch* b, int nsub, int forward_only, const int32_t* mask,
 }
 // Round 1 had a separate wide-output kernel that could be pipelined under the next step.  Every field is now written by
 // the phase that produces it, so there is nothing to pipeline or join: both calls are accepted and do nothing.
+int myo_batch_set_count_aware(myo_batch* b, int on) {
+  if (!b) return fail(MYO_ERR_ARG, "null batch");
+  b->count_aware = on != 0;
+  return MYO_OK;
+}
 int myo_batch_set_pipelined(myo_batch* b, int on) { (void)on; return b ? MYO_OK : fail(MYO_ERR_ARG, "null batch"); }
 int myo_outputs_join(myo_batch* b, void* stream) { (void)stream; return b ? MYO_OK : fail(MYO_ERR_ARG, "null batch"); }
 int myo_forward(myo_batch* b, void* stream) { return launch(b, 0, 1, nullptr, 0, stream); }

@@ -1273,7 +1273,9 @@ enum { E_D = 0, E_AREF, E_JAR, E_JV, E_FORCE, E_DESC0, E_COEF, E_DESC1, E_POS, E
 // ------------------------------------------------------------------------------------------ contact / efc outputs
 // (efc_force and solver_niter, the results of the solve, are written by finishKernel: these records are complete once the
 // rows exist, and go out while the solver runs)
-__device__ __noinline__ void writeConstraintOutputs(int slot, int fslot, SP sm, Tm t, World W, int ncon, int nefc) {
+// live_only (myo_batch_set_count_aware): only the records of the contacts / rows that exist are written, the padding up to
+// nconmax / njmax keeps whatever the buffers held
+__device__ __noinline__ void writeConstraintOutputs(int slot, int fslot, SP sm, Tm t, World W, int ncon, int nefc, bool live_only) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L; const FieldPtrs& F = tP[fslot].F;
   const int nv = D.nv, ncm = D.nconmax, njm = D.njmax;
   void* p;
@@ -1286,7 +1288,7 @@ __device__ __noinline__ void writeConstraintOutputs(int slot, int fslot, SP sm, 
   void* cinc = F.p[MYO_F_CONTACT_INCLUDEMARGIN]; void* cfri = F.p[MYO_F_CONTACT_FRICTION]; void* csr = F.p[MYO_F_CONTACT_SOLREF];
   void* csi = F.p[MYO_F_CONTACT_SOLIMP];
   if (cg || cdim || cadr || cdist || cpos || cfr || cinc || cfri || csr || csi) {
-    TFOR(c, ncm) {
+    TFOR(c, live_only ? ncon : ncm) {
       const bool on = c < ncon;
       auto cr = sm + L.con + 12 * c;
       const int prw = on ? __float_as_int(cr[7]) : 0, pr = CON_PAIR(prw), sw = CON_SWAP(prw);
@@ -1314,7 +1316,7 @@ __device__ __noinline__ void writeConstraintOutputs(int slot, int fslot, SP sm, 
   void* epos = F.p[MYO_F_EFC_POS]; void* emar = F.p[MYO_F_EFC_MARGIN]; void* eD = F.p[MYO_F_EFC_D]; void* earef = F.p[MYO_F_EFC_AREF];
   void* etyp = F.p[MYO_F_EFC_TYPE]; void* eJ = F.p[MYO_F_EFC_J];
   if (epos || emar || eD || earef || etyp || eJ) {
-    TFOR(r, njm) {
+    TFOR(r, live_only ? nefc : njm) {
       const bool on = r < nefc;
       if (epos) OUTF(epos, r) = on ? EFC(E_POS, r) : 0.f;
       if (emar) OUTF(emar, r) = on ? EFC(E_MARGIN, r) : 0.f;

@@ -15,7 +15,7 @@ void myo_make_layout(DevModel& D, int nconmax_req, int njmax_req, SmemLayout& L)
 // The kernels of the pipeline (tile.cu, lane = world): one entry per phase
 enum { MYO_K_KIN = 0, MYO_K_TENDON, MYO_K_INERTIA, MYO_K_COLLIDE, MYO_K_VELACT, MYO_K_FINISH, MYO_K_CONOUT, MYO_K_NEWTON, MYO_K_COLLIDE_MPR, MYO_K_COLLIDE_COMPACT, MYO_K_MAKECON, MYO_K_POSOUT, MYO_K_TENOUT, MYO_K_COMPACT_MAKECON };
 enum { MYO_KIN_LOAD = 1, MYO_KIN_RESET = 2, MYO_KIN_CHECK = 4 };                 // flags of MYO_K_KIN
-enum { MYO_FIN_EULER = 1, MYO_FIN_STATE = 2, MYO_FIN_WARM = 4, MYO_FIN_ACC = 8 };  // flags of MYO_K_FINISH
+enum { MYO_FIN_EULER = 1, MYO_FIN_STATE = 2, MYO_FIN_WARM = 4, MYO_FIN_ACC = 8, MYO_FIN_LIVE = 16 };  // flags of MYO_K_FINISH
 int myo_tile_upload(int slot, const DevModel& D, const SmemLayout& L, const FieldPtrs& F, const TileAux& X, void* stream);
 int myo_nop_launch(void* stream);
 int myo_tile_launch(int kernel, int slot, int fslot, int nworld, const int* mask, int flags, float* scratch, void* stream);
@@ -34,6 +34,7 @@ struct myo_batch {
   int slot;      // constant-memory parameter slot
   bool dirty;    // parameters changed since the last upload
   bool conout;   // some contact / constraint record field is bound: conoutKernel runs
+  bool count_aware = false;   // myo_batch_set_count_aware: the padding of contact_* / efc_* past ncon / nefc is not written
   void* wrap_cleared[2] = {nullptr, nullptr};   // wrap_obj / wrap_xpos buffers already zeroed once (api.cu)
   float* scratch; // per-world intermediates, tile-blocked: [tiles][L.total][32]
   TileAux X;      // work list of the convex narrow phase

@@ -47,7 +47,7 @@
 namespace {
 
 enum { KIN_LOAD = 1, KIN_RESET = 2, KIN_CHECK = 4 };
-enum { FIN_EULER = 1, FIN_STATE = 2, FIN_WARM = 4, FIN_ACC = 8 };
+enum { FIN_EULER = 1, FIN_STATE = 2, FIN_WARM = 4, FIN_ACC = 8, FIN_LIVE = 16 };   // FIN_LIVE: efc_force rows up to nefc only (count-aware batch)
 enum { WS_STATUS = 0, WS_TIME = 1, WS_SKIP = 2 };
 
 struct Ctx { SP sm; Tm t; World W; bool live; };
@@ -1317,12 +1317,13 @@ __device__ __noinline__ void finishTile(int slot, int fslot, SP sm, Tm t, World 
     if ((o = Fo.p[MYO_F_QFRC_INVERSE])) TFOR(i, nv) OUTF(o, i) = 0.f;
     if ((o = Fo.p[MYO_F_EFC_FORCE])) {
       const int nefc = __float_as_int(sm[L.counts + 1]);
-      for (int r0 = t.tl; r0 < D.njmax; r0 += 8 * t.nw) {   // (eight loads in flight)
+      const int rtop = (flags & FIN_LIVE) ? nefc : D.njmax;
+      for (int r0 = t.tl; r0 < rtop; r0 += 8 * t.nw) {   // (eight loads in flight)
         float v[8];
 #pragma unroll
         for (int u = 0; u < 8; u++) v[u] = r0 + u * t.nw < nefc ? EFC(E_FORCE, r0 + u * t.nw) : 0.f;
 #pragma unroll
-        for (int u = 0; u < 8; u++) if (r0 + u * t.nw < D.njmax) OUTF(o, r0 + u * t.nw) = v[u];
+        for (int u = 0; u < 8; u++) if (r0 + u * t.nw < rtop) OUTF(o, r0 + u * t.nw) = v[u];
       }
     }
     if ((o = Fo.p[MYO_F_SOLVER_NITER]) && t.tl == 0) OUTI(o, 0) = __float_as_int(sm[L.counts + 2]);
@@ -1509,14 +1510,14 @@ __global__ void __launch_bounds__(32 * MAXW, MINB_NEWTON) newtonKernel(int slot,
 // ------------------------------------------------------------------------------------------ conout: contact / constraint records
 // contact_* and efc_* (padded to nconmax / njmax, efc_J expanded to dense rows): pure stores, no ordering between items, so
 // the items are striped over the warps of gridDim.y CTAs per tile.
-__global__ void __launch_bounds__(256) conoutKernel(int slot, int fslot, int nworld, const int* __restrict__ mask, float* __restrict__ scratch) {
+__global__ void __launch_bounds__(256) conoutKernel(int slot, int fslot, int nworld, const int* __restrict__ mask, int live_only, float* __restrict__ scratch) {
   const SmemLayout& L = tP[slot].L;
   Timeline tline(slot, MYO_K_CONOUT);
   Ctx c = tileCtx(slot, nworld, mask, scratch);
   if (!c.live) return;
   Tm t; t.nw = c.t.nw * gridDim.y; t.tl = blockIdx.y * c.t.nw + c.t.tl;
   SP sm = c.sm;
-  writeConstraintOutputs(slot, fslot, sm, t, c.W, __float_as_int(sm[L.counts]), __float_as_int(sm[L.counts + 1]));
+  writeConstraintOutputs(slot, fslot, sm, t, c.W, __float_as_int(sm[L.counts]), __float_as_int(sm[L.counts + 1]), live_only != 0);
 }
 
 // known-answer hook for the rotation helpers above (tests/: reference KATs of myosuite/utils/quat_math.py)
@@ -1594,13 +1595,13 @@ int myo_tile_launch(int kernel, int slot, int fslot, int nworld, const int* mask
           configured[dev] = shmem;
         }
       }
-      newtonKernel<<<tiles, 32 * nwNew, shmem, st>>>(slot, fslot, nworld, mask, flags & 1, use_smem, (flags & 32) ? ((flags >> 1) & 15) : -1, scratch);
+      newtonKernel<<<tiles, 32 * nwNew, shmem, st>>>(slot, fslot, nworld, mask, flags & 1, use_smem, (flags & 32) ? (((flags >> 1) & 15) | ((flags & 64) ? 16 : 0)) : -1, scratch);
     } break;
     case MYO_K_TENOUT: tenoutKernel<<<mask ? tiles : std::min(tiles, outGrid), 32 * nwPos, 0, st>>>(slot, fslot, nworld, mask, scratch); break;
     case MYO_K_POSOUT: posoutKernel<<<mask ? tiles : std::min(tiles, outGrid), 32 * nwPos, 0, st>>>(slot, fslot, nworld, mask, scratch); break;
     case MYO_K_COMPACT_MAKECON: compactMakeconKernel<<<tiles, 32 * nwMak, 0, st>>>(slot, nworld, mask, scratch); break;
     case MYO_K_MAKECON: makeconKernel<<<tiles, 32 * nwMak, 0, st>>>(slot, nworld, mask, scratch); break;
-    case MYO_K_CONOUT: conoutKernel<<<dim3(tiles, yOut), 32 * nwOut, 0, st>>>(slot, fslot, nworld, mask, scratch); break;
+    case MYO_K_CONOUT: conoutKernel<<<dim3(tiles, yOut), 32 * nwOut, 0, st>>>(slot, fslot, nworld, mask, flags & 1, scratch); break;
     default: return -1;
   }
   return cudaPeekAtLastError() == cudaSuccess ? 0 : -1;

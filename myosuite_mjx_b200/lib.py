@@ -54,6 +54,7 @@ def lib():
         L.myo_batch_ctas_per_sm.argtypes = [vp]
         L.myo_batch_engine.argtypes = [vp]
         L.myo_batch_set_pipelined.argtypes = [vp, i32]
+        L.myo_batch_set_count_aware.argtypes = [vp, i32]
         L.myo_outputs_join.argtypes = [vp, vp]
         L.myo_field_count.restype = i64
         L.myo_field_count.argtypes = [vp, i32]
@@ -84,4 +85,4 @@ EXPORTS = ["myo_model_create", "myo_model_destroy", "myo_batch_create", "myo_bat
            "myo_batch_njmax", "myo_batch_smem_bytes", "myo_batch_team", "myo_batch_ctas_per_sm", "myo_batch_engine", "myo_batch_set_pipelined", "myo_outputs_join", "myo_field_count", "myo_field_itemsize", "myo_field_is_int", "myo_field_name", "myo_batch_bind",
            "myo_forward", "myo_forward_masked", "myo_forward_posvel", "myo_step", "myo_reset", "myo_step_host", "myo_launch_count", "myo_last_error", "myo_kat_quat",
            "myo_env_create", "myo_env_destroy", "myo_env_field_count", "myo_env_bind", "myo_env_seed", "myo_env_reset", "myo_env_step",
-           "myo_env_forward", "myo_kinematics_noalloc"]
+           "myo_env_forward", "myo_kinematics_noalloc", "myo_batch_set_count_aware"]

@@ -165,6 +165,12 @@ class Data:
         self.__dict__["_pipelined"] = bool(on)
         return self
 
+    def set_count_aware(self, on=True):
+        """Opt in to count-aware outputs (include/myostep.h, myo_batch_set_count_aware): `contact_*` / `efc_*` are written only
+        up to `ncon` / `nefc`; the padding up to nconmax / njmax is left as it is (read those fields with `[:ncon]` / `[:nefc]`)."""
+        _lib.check(_lib.lib().myo_batch_set_count_aware(self._h, 1 if on else 0))
+        return self
+
     def join(self):
         if self.__dict__.get("_pipelined"):
             _lib.check(_lib.lib().myo_outputs_join(self._h, _stream()))

@@ -187,3 +187,36 @@ def test_benchmarked_shape_matches_oracle(models):
         assert np.abs(v1[i] - o.qvel).max() < 1e-3 * max(1.0, np.abs(o.qvel).max())
         o.step(9)
         assert np.abs(q10[i] - o.qpos).max() < 2e-3, f"world {w}: 10-step drift {np.abs(q10[i] - o.qpos).max()}"
+
+
+def test_count_aware_outputs_write_live_records_only(models):
+    """myo_batch_set_count_aware: the live contact / row records equal the default path's bit for bit, the padding is untouched
+    (a sentinel the test put there survives), everything else is identical."""
+    import torch
+    from myosuite_mjx_b200 import mjx
+    m = models("hand")
+    nw = 96
+    qpos, qvel, act, ctrl = parity.random_state(m, nw, 77, qpos_spread=0.9)
+    model = mjx.put_model(m)
+    init = dict(qpos=qpos, qvel=qvel, act=act, ctrl=ctrl)
+    a = mjx.put_data(model, init, nworld=nw, fields="all")
+    b = mjx.put_data(model, init, nworld=nw, fields="all").set_count_aware(True)
+    names = ["efc_j", "efc_pos", "efc_margin", "efc_d", "efc_aref", "efc_force", "contact_dist", "contact_pos", "contact_frame", "contact_friction"]
+    for k in names:
+        b.storage(k).fill_(-7.5)
+    for k in ("efc_type", "contact_geom", "contact_dim", "contact_efc_address"):
+        b.storage(k).fill_(-75)
+    mjx.step(model, a, 1); mjx.step(model, b, 1)
+    torch.cuda.synchronize()
+    assert torch.equal(a.qpos, b.qpos) and torch.equal(a.qacc, b.qacc) and torch.equal(a.nefc, b.nefc) and torch.equal(a.ncon, b.ncon)
+    nefc, ncon = a.nefc[:, 0].cpu().numpy(), a.ncon[:, 0].cpu().numpy()
+    assert nefc.max() > 0 and ncon.max() > 0 and nefc.min() < a.efc_type.shape[1]
+    nv = m.nv
+    for w in range(nw):
+        n, c = int(nefc[w]), int(ncon[w])
+        assert torch.equal(a.efc_j[w].reshape(-1, nv)[:n], b.efc_j[w].reshape(-1, nv)[:n]) and bool((b.efc_j[w].reshape(-1, nv)[n:] == -7.5).all())
+        for k in ("efc_pos", "efc_margin", "efc_d", "efc_aref", "efc_force"):
+            assert torch.equal(getattr(a, k)[w, :n], getattr(b, k)[w, :n]) and bool((getattr(b, k)[w, n:] == -7.5).all()), k
+        assert torch.equal(a.efc_type[w, :n], b.efc_type[w, :n]) and bool((b.efc_type[w, n:] == -75).all())
+        assert torch.equal(a.contact_dist[w, :c], b.contact_dist[w, :c]) and bool((b.contact_dist[w, c:] == -7.5).all())
+        assert torch.equal(a.contact_geom[w].reshape(-1, 2)[:c], b.contact_geom[w].reshape(-1, 2)[:c]) and bool((b.contact_geom[w].reshape(-1, 2)[c:] == -75).all())
