@@ -790,11 +790,11 @@ template <int NB> __device__ __forceinline__ void syrkBlocks(int slot, SP sm, Tm
       }
   }
 }
-// H = M + J^T D_active J (lower triangle, row-packed) and its Cholesky factor; Hd receives the factor's diagonal.
+// H = M + J^T D_active J (lower triangle, row-packed); the unfactored matrix is also saved for the later passes' updates.
 // Contacts enter through their base rows (normal, tangents, torsion): with W the small symmetric weight matrix of a
-// contact's active pyramid rows in base-row space, J^T D J = Jb^T (W Jb) =: Jb^T U, a dense [nv x nbase] x [nbase x nv]
-// product over the tile's nbase = maxbase * nconT base rows, done in 4 x 4 register blocks of H (one block per warp at a
-// time, the warps stream the same rows of U and Jb through L1 together).
+// contact's active pyramid rows in base-row space, J^T D J = Jb^T (W Jb), a dense [nv x nbase] x [nbase x nv] product over
+// the tile's nbase = maxbase * nconT base rows, done in 4 x 4 register blocks of H (syrkBlocks: one block per warp at a
+// time, W Jb formed in registers, the warps stream the same rows of Jb through L1 together).
 __device__ __noinline__ void hessianAssemble(int slot, SP sm, Tm t, SP H, int ncon, int nconT, int nefc) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
   const int nv = D.nv, nb = D.maxbase, nw = t.nw;
@@ -863,8 +863,8 @@ __device__ __noinline__ void hessianAssemble(int slot, SP sm, Tm t, SP H, int nc
   TFOR(i, TRI(nv)) sm[L.Hsave + i] = H[i];   // keep the unfactored matrix: later passes of the tile update it (hessianUpdate)
 }
 // Later Newton passes of a tile: only the rows whose active state flipped in the last line search change H, each by a
-// sparse rank-1 term +-D_r J_r^T J_r (the flags were left in E_JV by the row update).  One warp applies them, every lane
-// walking its own flipped rows -- a few hundred instructions against the dense rebuild's ~10^5.
+// rank-1 term +-D_r J_r^T J_r (the flags were left in E_JV by the row update): per-lane flip lists, then the tile's warps
+// apply them two at a time as dense vectors staged in shared memory (va, vb: two nv-vectors that are free here).
 __device__ __noinline__ void hessianUpdate(int slot, SP sm, Tm t, SP H, int nefc, SP va, SP vb) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
   const int nv = D.nv, nw = t.nw;
@@ -1442,7 +1442,7 @@ __global__ void __launch_bounds__(32 * MAXW, MINB_MAKECON) compactMakeconKernel(
   if (t.tl == 0) { sm[L.counts + 1] = __int_as_float(nefc); sm[L.wstate + WS_STATUS] = __int_as_float(status); }
 }
 static inline size_t newtonSmemFloats(int nv) { return (size_t)(TRI(nv) + 7 * nv) * 32; }   // (+ the LDL solve's index tables, myo_tile_launch)
-#define NEWTON_SMEM_MAX (190 * 1024)   // + ~31 KB of static reduction / scan buffers <= 227 KB per CTA
+#define NEWTON_SMEM_MAX (190 * 1024)   // + ~9 KB of static reduction / scan buffers <= 227 KB per CTA
 __global__ void __launch_bounds__(32 * MAXW, MINB_NEWTON) newtonKernel(int slot, int fslot, int nworld, const int* __restrict__ mask, int check_acc,
                                                     int use_smem, int fin, float* __restrict__ scratch) {
   const DevModel& D = tP[slot].D; const SmemLayout& L = tP[slot].L;
