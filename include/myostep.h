@@ -76,6 +76,13 @@ typedef struct myo_model_desc {
   int32_t nsensor;
   const int32_t *sensor_objid, *site_type;
   const double *site_size;
+  /* convex hulls of the mesh geoms (row n2: mesh-convex collision of the object_sim contact*.stl pieces, reference
+   * myosuite/simhive/object_sim/common.xml:10-20): geom_dataid[g] = mesh of geom g or -1; mesh m's hull vertices are
+   * mesh_vert[3 * mesh_vertadr[m] ...), mesh_vertnum[m] of them, in the geom's own frame (MuJoCo: re-centred on the centre of
+   * mass / principal axes).  Collision uses the hull, as MuJoCo does. */
+  int32_t nmesh, nmeshvert;
+  const int32_t *mesh_vertadr, *mesh_vertnum, *geom_dataid;
+  const double *mesh_vert;
 } myo_model_desc;
 
 /* status codes */

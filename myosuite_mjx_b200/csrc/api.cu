@@ -94,7 +94,7 @@ int checkReady(myo_batch* b) {
   if (!b) return fail(MYO_ERR_ARG, "null batch");
   for (int f : kStateFields)
     if (!b->F.p[f]) return fail(MYO_ERR_UNBOUND, std::string("state field not bound: ") + kFieldNames[f]);
-  if (cudaSetDevice(b->model->device) != cudaSuccess) return fail(MYO_ERR_CUDA, "cudaSetDevice failed");
+  if (cudaSetDevice(b->device) != cudaSuccess) return fail(MYO_ERR_CUDA, "cudaSetDevice failed");
   return MYO_OK;
 }
 }  // namespace
@@ -137,7 +137,7 @@ int myo_batch_create(const myo_model* m, int nworld, int nconmax, int njmax, myo
   if (!m || !out || nworld <= 0) return fail(MYO_ERR_ARG, "bad argument");
   if (cudaSetDevice(m->device) != cudaSuccess) return fail(MYO_ERR_CUDA, "cudaSetDevice failed");
   myo_batch* b = new myo_batch();
-  b->model = m; b->D = m->D; b->nworld = nworld; b->slot = -1; b->dirty = true;
+  b->model = m; b->D = m->D; b->nworld = nworld; b->slot = -1; b->dirty = true; b->device = m->device;
   {
     std::lock_guard<std::mutex> lk(g_slot_mutex);
     for (int i = 0; i < MYO_PARAM_SLOTS; i++) if (!g_slot_used[i]) { b->slot = i; g_slot_used[i] = true; break; }
@@ -185,7 +185,7 @@ int myo_batch_create(const myo_model* m, int nworld, int nconmax, int njmax, myo
 }
 void myo_batch_destroy(myo_batch* b) {
   if (!b) return;
-  cudaSetDevice(b->model->device);
+  if (cudaSetDevice(b->device) != cudaSuccess) cudaGetLastError();   // (b->model may be gone already; never leave an error pending for the next launch check)
   for (void* p : b->owned) cudaFree(p);
   for (int i = 0; i < 5; i++) if (b->side[i]) { cudaStreamSynchronize((cudaStream_t)b->side[i]); cudaStreamDestroy((cudaStream_t)b->side[i]); }
   for (int i = 0; i < 10; i++) if (b->ev[i]) cudaEventDestroy((cudaEvent_t)b->ev[i]);
@@ -275,13 +275,15 @@ static int launchPhases(myo_batch* b, int nsub, int forward_only, const int32_t*
   auto tile = [&](int k, int fslot, int flags) {
     g_launches++;
     int r = myo_tile_launch(k, slot, fslot, nw, mask, flags, scr, cur);
+    if (r != 0 && debug_sync) fprintf(stderr, "[myostep] launch of tile kernel %d failed (flags %d): %s\n", k, flags, cudaGetErrorString(cudaPeekAtLastError()));
     if (debug_sync && r == 0) {
       const cudaError_t e = cudaStreamSynchronize((cudaStream_t)cur);
       if (e != cudaSuccess) { fprintf(stderr, "[myostep] tile kernel %d failed: %s\n", k, cudaGetErrorString(e)); r = -1; }
     }
     return r;
   };
-  bool ok = true;
+  bool ok = true; bool reported_ = false;
+#define DBGL() do { if (!ok && debug_sync && !reported_) { fprintf(stderr, "[myostep] launchPhases: first failure before api.cu line %d: %s\n", __LINE__, cudaGetErrorString(cudaPeekAtLastError())); reported_ = true; } } while (0)
   // mj_collision = broad phase + closed-form pairs, the listed convex pairs one per lane, ordered compaction
   // at_mark(): after kernel `mark` of the chain (1 = broad phase, 2 = convex narrow phase); fuse_rows: the compaction runs as
   // the head of the constraint-row kernel (MYO_K_COMPACT_MAKECON), launched by the caller
@@ -313,6 +315,7 @@ static int launchPhases(myo_batch* b, int nsub, int forward_only, const int32_t*
       auto E = [&](int i) { return (cudaEvent_t)b->ev[i]; };
       const cudaStream_t main = (cudaStream_t)stream;
       ok &= cudaEventRecord(E(0), main) == cudaSuccess;
+      DBGL();
       for (int i = 0; i < 4; i++) ok &= cudaStreamWaitEvent(S(i), E(0), 0) == cudaSuccess;
       // output stream (lowest priority): the position stage's fields now, the contact / constraint records once the rows exist
       static const int ndelay = getenv("MYO_DELAY") ? atoi(getenv("MYO_DELAY")) : 1;   // developer knob
@@ -328,8 +331,10 @@ static int launchPhases(myo_batch* b, int nsub, int forward_only, const int32_t*
       const bool fuse_rows = fuse_compact && makecon_early && b->D.npair > 0;
       auto rows = [&](cudaStream_t on) {   // on the stream `cur` = `on`
         ok &= tile(fuse_rows ? MYO_K_COMPACT_MAKECON : MYO_K_MAKECON, fslot, 0) == 0;
+      DBGL();
         if (conout && !conout_late) {
           ok &= cudaEventRecord(E(3), on) == cudaSuccess && cudaStreamWaitEvent(S(3), E(3), 0) == cudaSuccess;
+      DBGL();
           void* keep = cur; cur = b->side[3]; ok &= tile(MYO_K_CONOUT, fslot, b->count_aware ? 1 : 0) == 0; cur = keep;
         }
       };
@@ -338,32 +343,41 @@ static int launchPhases(myo_batch* b, int nsub, int forward_only, const int32_t*
       int collide_mark = posout && !(out_late & 2) ? posout_after : 0;
       cur = b->side[0]; ok &= collide(fslot, collide_mark, [&]() {
         ok &= cudaEventRecord(E(7), S(0)) == cudaSuccess && cudaStreamWaitEvent(S(3), E(7), 0) == cudaSuccess;
+      DBGL();
         void* keep = cur; cur = b->side[3]; ok &= tile(MYO_K_POSOUT, fslot, 0) == 0; cur = keep;
       }, fuse_rows);
       for (int i = 0; i < ndelay; i++) { g_launches += 2; ok &= myo_nop_launch(b->side[1]) == 0 && myo_nop_launch(b->side[2]) == 0; }
       cur = b->side[1]; ok &= tile(MYO_K_TENDON, fslot, 0) == 0;
       if (posout && !(out_late & 1)) {   // ten_length, ten_J, path points: on the output stream, behind the tendon stage
         ok &= cudaEventRecord(E(6), S(1)) == cudaSuccess && cudaStreamWaitEvent(S(3), E(6), 0) == cudaSuccess;
+      DBGL();
         cur = b->side[3]; ok &= tile(MYO_K_TENOUT, fslot, 0) == 0; cur = b->side[1];
       }
       cur = b->side[2]; ok &= tile(MYO_K_INERTIA, fslot, (forward_only ? 0 : 1) | inertiaStage(b->D)) == 0;
       ok &= cudaEventRecord(E(2), S(2)) == cudaSuccess && cudaStreamWaitEvent(S(1), E(2), 0) == cudaSuccess;
+      DBGL();
       cur = b->side[1]; ok &= tile(MYO_K_VELACT, fslot, velactStage(b->D)) == 0;
       ok &= cudaEventRecord(E(5), S(1)) == cudaSuccess;
+      DBGL();
       cur = b->side[0];   // (after the tendon branch in host order: the output stream then holds posout, tenout, conout in that order)
       if (makecon_early) rows(S(0));
       ok &= cudaEventRecord(E(1), S(0)) == cudaSuccess;
+      DBGL();
       cur = stream;
       ok &= cudaStreamWaitEvent(main, E(1), 0) == cudaSuccess && cudaStreamWaitEvent(main, E(5), 0) == cudaSuccess;
+      DBGL();
       if (!makecon_early) rows(main);
       if (posout && out_late) {
         ok &= cudaEventRecord(E(8), main) == cudaSuccess && cudaStreamWaitEvent((cudaStream_t)b->side[4], E(8), 0) == cudaSuccess;
+      DBGL();
       }
       const int fin = (forward_only ? 0 : MYO_FIN_EULER) | (last && (!forward_only || do_reset) ? MYO_FIN_STATE : 0) | (last ? MYO_FIN_WARM | MYO_FIN_ACC | (b->count_aware ? MYO_FIN_LIVE : 0) : 0);
       static const bool fuse_finish = !(getenv("MYO_FUSE_FINISH") && atoi(getenv("MYO_FUSE_FINISH")) == 0);   // developer knob
       ok &= tile(MYO_K_NEWTON, fslot, (forward_only ? 0 : 1) | (fuse_finish ? (fin << 1) | 32 : 0) | (b->count_aware ? 64 : 0) | (b->D.nv << 8)) == 0;
+      DBGL();
       if (conout && conout_late) {
         ok &= cudaEventRecord(E(3), main) == cudaSuccess && cudaStreamWaitEvent(S(3), E(3), 0) == cudaSuccess;
+      DBGL();
         cur = b->side[3]; ok &= tile(MYO_K_CONOUT, fslot, b->count_aware ? 1 : 0) == 0; cur = stream;
       }
       if (!fuse_finish) ok &= tile(MYO_K_FINISH, fslot, fin) == 0;
@@ -373,6 +387,7 @@ static int launchPhases(myo_batch* b, int nsub, int forward_only, const int32_t*
         if (out_late & 2) ok &= tile(MYO_K_POSOUT, fslot, 0) == 0;
         cur = stream;
         ok &= cudaEventRecord(E(9), (cudaStream_t)b->side[4]) == cudaSuccess && cudaStreamWaitEvent(main, E(9), 0) == cudaSuccess;
+      DBGL();
       }
       if (conout || posout) ok &= cudaEventRecord(E(4), S(3)) == cudaSuccess && cudaStreamWaitEvent(main, E(4), 0) == cudaSuccess;
       continue;

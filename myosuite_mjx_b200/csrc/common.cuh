@@ -1063,7 +1063,7 @@ __device__ __forceinline__ double norm3(d3 a) { return sqrt(dot(a, a)); }
 __device__ __forceinline__ d3 unit3(d3 a) { const double q = dot(a, a); return q < 1e-30 ? mkd(1.0, 0.0, 0.0) : a * rsqrt(q); }   // (one rsqrt instead of sqrt + divide: these sit on the portal iteration's dependent chain)
 // (the rotation is copied into the record once: the support function runs tens of times per pair; it and mprSup are
 // inlined so that the portal's support points stay in registers instead of going through the stack)
-struct Shape { int type; d3 pos; float mat[9]; d3 size; double margin; };
+struct Shape { int type; d3 pos; float mat[9]; d3 size; double margin; const float* verts; int nvert; };   // verts: hull of a mesh geom
 __device__ __forceinline__ void shapeMat(Shape& s, SP R) {
 #pragma unroll
   for (int i = 0; i < 9; i++) s.mat[i] = R[i];
@@ -1085,6 +1085,14 @@ __device__ __forceinline__ d3 supportPt(const Shape& s, d3 dir) {
       r.z = d.z >= 0.0 ? s.size.y : -s.size.y;
     } break;
     case G_BOX: r = mkd(d.x >= 0.0 ? s.size.x : -s.size.x, d.y >= 0.0 ? s.size.y : -s.size.y, d.z >= 0.0 ? s.size.z : -s.size.z); break;
+    case G_MESH: {   // the hull vertex farthest along d (MuJoCo climbs the hull's graph to the same vertex; first one wins a tie)
+      double best = -1e300;
+      for (int i = 0; i < s.nvert; i++) {
+        const double vx = s.verts[3 * i], vy = s.verts[3 * i + 1], vz = s.verts[3 * i + 2];
+        const double v = vx * d.x + vy * d.y + vz * d.z;
+        if (v > best) { best = v; r = mkd(vx, vy, vz); }
+      }
+    } break;
     default: break;
   }
   return mkd(R[0] * r.x + R[1] * r.y + R[2] * r.z, R[3] * r.x + R[4] * r.y + R[5] * r.z, R[6] * r.x + R[7] * r.y + R[8] * r.z) + s.pos + dir * s.margin;
@@ -1213,6 +1221,7 @@ template <bool CONVEX> __device__ __noinline__ int collidePair(int slot, SP sm, 
       }
     } else {
       Shape s; s.type = t2; s.pos = mkd(p2.x, p2.y, p2.z); shapeMat(s, R2); s.size = mkd(sz2.x, sz2.y, sz2.z); s.margin = 0.0;
+      s.verts = D.mesh_vert + 3 * D.cg_meshadr[c2]; s.nvert = D.cg_meshnum[c2];
       const d3 spd = supportPt(s, mkd(-ax1.x, -ax1.y, -ax1.z));
       const f3 sp = mk3((float)spd.x, (float)spd.y, (float)spd.z);
       const float dist = (float)((spd.x - p1.x) * ax1.x + (spd.y - p1.y) * ax1.y + (spd.z - p1.z) * ax1.z);
@@ -1242,6 +1251,7 @@ template <bool CONVEX> __device__ __noinline__ int collidePair(int slot, SP sm, 
     Shape A, B;
     A.type = t1; A.pos = mkd(p1.x, p1.y, p1.z); shapeMat(A, R1); A.size = mkd(sz1.x, sz1.y, sz1.z); A.margin = 0.5 * (double)margin;
     B.type = t2; B.pos = mkd(p2.x, p2.y, p2.z); shapeMat(B, R2); B.size = mkd(sz2.x, sz2.y, sz2.z); B.margin = 0.5 * (double)margin;
+    A.verts = D.mesh_vert + 3 * D.cg_meshadr[c1]; A.nvert = D.cg_meshnum[c1]; B.verts = D.mesh_vert + 3 * D.cg_meshadr[c2]; B.nvert = D.cg_meshnum[c2];
     double depth; d3 nrm, pos;
     if (!mprPenetration(A, B, 1e-6, 50, &depth, &nrm, &pos, filter)) return 0;
     if (filter) return -1;

@@ -91,6 +91,8 @@ struct DevModel {
   // ---- collision
   const int *cg_geom, *cg_type, *cg_frame, *cg_body;
   const float *cg_lpos, *cg_lmat, *cg_size, *cg_rbound, *cg_invweight;   // invweight: [ncg][2]
+  const int *cg_meshadr, *cg_meshnum;          // [ncg] hull vertices of a mesh collision geom in mesh_vert (0, 0 for primitives)
+  const float *mesh_vert;                      // [nmeshvert][3]
   const int *pair_cg1, *pair_cg2, *pair_dim;
   const float *pair_prm;                       // [npair][16]: margin, gap, friction[5], solref[2], sanitised solimp[5], K, B
   // ---- constraints

@@ -420,7 +420,7 @@ int myo_env_create(myo_batch* b, const myo_env_desc* d, myo_env** out) {
     return myo_fail(MYO_ERR_ARG, "reafferentation needs the EPL and EIP actuator ids");
   if (d->kind == MYO_ENV_POSE)
     for (int k = 0; k < d->ntarget; k++) if (d->target_qposadr[k] < 0 || d->target_qposadr[k] >= D.nq) return myo_fail(MYO_ERR_ARG, "target_qposadr out of range");
-  if (cudaSetDevice(b->model->device) != cudaSuccess) return myo_fail(MYO_ERR_CUDA, "cudaSetDevice failed: libmyostep has no CPU fallback");
+  if (cudaSetDevice(b->device) != cudaSuccess) return myo_fail(MYO_ERR_CUDA, "cudaSetDevice failed: libmyostep has no CPU fallback");
   myo_env* e = new myo_env();
   e->b = b;
   EnvParams& P = e->P;
@@ -547,7 +547,7 @@ static int envReady(myo_env* e) {
         return myo_fail(MYO_ERR_UNBOUND, "randomize_shape writes geom_type_ovr, geom_size_ovr and geom_pos_ovr: bind them on the batch");
     }
   }
-  if (cudaSetDevice(e->b->model->device) != cudaSuccess) return myo_fail(MYO_ERR_CUDA, "cudaSetDevice failed: libmyostep has no CPU fallback");
+  if (cudaSetDevice(e->b->device) != cudaSuccess) return myo_fail(MYO_ERR_CUDA, "cudaSetDevice failed: libmyostep has no CPU fallback");
   return MYO_OK;
 }
 static void envRewardLaunch(const EnvParams& P, int advance, void* stream) {

@@ -32,6 +32,7 @@ struct myo_batch {
   FieldPtrs F;
   int nworld;
   int slot;      // constant-memory parameter slot
+  int device = 0;   // the model's device, kept here: a batch may be destroyed after its model (garbage collectors give no order)
   bool dirty;    // parameters changed since the last upload
   bool conout;   // some contact / constraint record field is bound: conoutKernel runs
   bool count_aware = false;   // myo_batch_set_count_aware: the padding of contact_* / efc_* past ncon / nefc is not written

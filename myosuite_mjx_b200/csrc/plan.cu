@@ -456,7 +456,7 @@ void myo_build_plan(const myo_model_desc& m, int nconmax_req, int njmax_req, Dev
   int maxbase = 1;
   {
     std::map<int, int> cgidx;
-    std::vector<int> cg_geom, cg_type, cg_frame, cg_body, p1, p2, pdim;
+    std::vector<int> cg_geom, cg_type, cg_frame, cg_body, cg_meshadr, cg_meshnum, p1, p2, pdim;
     std::vector<float> cg_lpos, cg_lmat, cg_size, cg_rbound, cg_invw, pprm;
     auto cg = [&](int g) {
       auto it = cgidx.find(g);
@@ -468,6 +468,9 @@ void myo_build_plan(const myo_model_desc& m, int nconmax_req, int njmax_req, Dev
       for (int k = 0; k < 9; k++) cg_lmat.push_back((float)R[k]);
       for (int k = 0; k < 3; k++) cg_size.push_back((float)m.geom_size[3 * g + k]);
       cg_rbound.push_back((float)m.geom_rbound[g]);
+      const int mesh = m.geom_type[g] == G_MESH ? m.geom_dataid[g] : -1;
+      if (m.geom_type[g] == G_MESH && (mesh < 0 || mesh >= m.nmesh || m.mesh_vertnum[mesh] < 4)) throw std::string("mesh collision geom without a convex hull (geom_dataid / mesh_vert)");
+      cg_meshadr.push_back(mesh >= 0 ? m.mesh_vertadr[mesh] : 0); cg_meshnum.push_back(mesh >= 0 ? m.mesh_vertnum[mesh] : 0);
       cg_invw.push_back((float)m.body_invweight0[2 * b]); cg_invw.push_back((float)m.body_invweight0[2 * b + 1]);
       return id;
     };
@@ -475,7 +478,6 @@ void myo_build_plan(const myo_model_desc& m, int nconmax_req, int njmax_req, Dev
       int t1 = m.geom_type[g1], t2 = m.geom_type[g2];
       if (t1 > t2) { std::swap(g1, g2); std::swap(t1, t2); }
       if (t1 == G_HFIELD || t2 == G_HFIELD) return;  // height fields: not supported, pair dropped
-      if (t1 == G_MESH || t2 == G_MESH) throw std::string("mesh collision geoms are not supported");
       if (t1 == G_PLANE && t2 == G_PLANE) return;
       if (dim != 1 && dim != 3 && dim != 4) throw std::string("contact condim must be 1, 3 or 4");
       maxbase = std::max(maxbase, dim);
@@ -577,6 +579,8 @@ void myo_build_plan(const myo_model_desc& m, int nconmax_req, int njmax_req, Dev
     }
     D.cg_geom = upload(cg_geom, owned); D.cg_type = upload(cg_type, owned); D.cg_frame = upload(cg_frame, owned); D.cg_body = upload(cg_body, owned);
     D.cg_lpos = upload(cg_lpos, owned); D.cg_lmat = upload(cg_lmat, owned); D.cg_size = upload(cg_size, owned); D.cg_rbound = upload(cg_rbound, owned);
+    D.cg_meshadr = upload(cg_meshadr, owned); D.cg_meshnum = upload(cg_meshnum, owned);
+    { std::vector<float> mv((size_t)3 * std::max(0, m.nmeshvert)); for (size_t i = 0; i < mv.size(); i++) mv[i] = (float)m.mesh_vert[i]; D.mesh_vert = upload(mv, owned); }
     D.cg_invweight = upload(cg_invw, owned); D.pair_cg1 = upload(p1, owned); D.pair_cg2 = upload(p2, owned); D.pair_dim = upload(pdim, owned);
     D.pair_prm = upload(pprm, owned);
   }

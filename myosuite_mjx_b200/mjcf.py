@@ -147,6 +147,25 @@ def mesh_mass_properties(tri):
     return vol, com, I
 
 
+def hull_vertices(points):
+    """Vertices of the convex hull of a point set (unique, in the hull's vertex order)."""
+    from scipy.spatial import ConvexHull
+    pts = np.unique(np.asarray(points, dtype=np.float64), axis=0)
+    return pts[ConvexHull(pts).vertices]
+
+
+def hull_triangles(points):
+    """Outward-oriented triangles of the convex hull of a point set."""
+    from scipy.spatial import ConvexHull
+    pts = np.unique(np.asarray(points, dtype=np.float64), axis=0)
+    h = ConvexHull(pts)
+    tri = pts[h.simplices]
+    n = np.cross(tri[:, 1] - tri[:, 0], tri[:, 2] - tri[:, 0])
+    flip = np.einsum("ij,ij->i", n, h.equations[:, :3]) < 0
+    tri[flip] = tri[flip][:, ::-1]
+    return tri
+
+
 # ---- XML loading ---------------------------------------------------------------------------------
 def _load_tree(path, main_dir):
     root = ET.parse(path).getroot()
@@ -307,6 +326,10 @@ class Model:
             for k in z.files:
                 v = z[k]
                 m.__dict__[k] = v.item() if v.ndim == 0 and v.dtype.kind in "iuf" else v
+        if "geom_dataid" not in m.__dict__:   # fixtures written before mesh colliders existed
+            m.nmesh, m.nmeshvert = 0, 0
+            m.mesh_vertadr = np.zeros(0, dtype=np.int32); m.mesh_vertnum = np.zeros(0, dtype=np.int32)
+            m.mesh_vert = np.zeros((0, 3)); m.geom_dataid = np.full(int(m.ngeom), -1, dtype=np.int32)
         return m
 
     def name2id(self, kind, name):
@@ -345,6 +368,7 @@ class _Compiler:
                         disableflags=0, noslip_iterations=0)
         self.defaults = _Defaults()
         self.meshes = {}
+        self.mesh_verts = {}
         self.mesh_cache = {}
         self.bodies = []
 
@@ -421,6 +445,8 @@ class _Compiler:
                 a = self.defaults.attrs("mesh", me, None)
                 name = a.get("name") or os.path.splitext(os.path.basename(a["file"]))[0]
                 self.meshes[name] = (a.get("file"), _floats(a.get("scale", "1 1 1"), 3))
+                if "vertex" in a:   # inline vertex list: the mesh is its convex hull (as in MuJoCo)
+                    self.mesh_verts[name] = _floats(a["vertex"]).reshape(-1, 3) * _floats(a.get("scale", "1 1 1"), 3)
 
         world = _Body()
         world.name = "world"
@@ -473,15 +499,26 @@ class _Compiler:
 
     # -- geoms
     def _mesh_props(self, name):
+        """(volume, centre of mass, principal inertia, principal-axes quaternion, hull vertices in the re-centred frame)"""
         if name not in self.mesh_cache:
             f, scale = self.meshes[name]
-            p = os.path.normpath(os.path.join(self.main_dir, self.comp["meshdir"], f))
-            if not p.lower().endswith(".stl"):
+            tri = None
+            if name in self.mesh_verts:
+                tri = hull_triangles(self.mesh_verts[name])
+            elif f is not None:
+                p = os.path.normpath(os.path.join(self.main_dir, self.comp["meshdir"], f))
+                if p.lower().endswith(".stl"):
+                    tri = load_stl(p, scale)
+            if tri is None:
                 self.mesh_cache[name] = None  # .msh/.obj scene props: static, visual only
             else:
-                vol, com, I = mesh_mass_properties(load_stl(p, scale))
+                vol, com, I = mesh_mass_properties(tri)
                 diag, q = principal_axes(I)
-                self.mesh_cache[name] = (vol, com, diag, q)
+                # collision geometry = the convex hull (MuJoCo: mjCMesh::MakeGraph), in the mesh frame MuJoCo re-centres on the
+                # centre of mass and the principal axes
+                hv = hull_vertices(tri.reshape(-1, 3))
+                hv = (hv - com) @ quat_to_mat(q)
+                self.mesh_cache[name] = (vol, com, diag, q, hv)
         return self.mesh_cache[name]
 
     def _geom(self, a, need_mass):
@@ -532,7 +569,8 @@ class _Compiler:
             props = self._mesh_props(a["mesh"]) if (need_mass or a["mesh"] in self.mesh_cache or self.meshes[a["mesh"]][0].lower().endswith(".stl")) else None
             rbound = 0.0
             if props is not None:
-                mvol, mcom, mdiag, mq = props
+                mvol, mcom, mdiag, mq, mhull = props
+                rbound = float(np.linalg.norm(mhull, axis=1).max())   # (geom_size stays zero: collision reads the hull)
                 # the mesh frame is re-centred on its centre of mass / principal axes
                 pos = pos + quat_to_mat(quat) @ mcom
                 quat = quat_mul(quat, mq)
@@ -545,7 +583,7 @@ class _Compiler:
         else:
             mass = float(a.get("density", 1000.0)) * vol
         g = dict(type=t, size=size, pos=pos, quat=quat / np.linalg.norm(quat), mass=mass, inertia=inertia_unit * mass,
-                 rbound=rbound, name=a.get("name", ""),
+                 rbound=rbound, name=a.get("name", ""), mesh=(a["mesh"] if t == GEOM_MESH and self._mesh_props(a["mesh"]) is not None else None),
                  contype=int(a.get("contype", 1)), conaffinity=int(a.get("conaffinity", 1)), condim=int(a.get("condim", 3)),
                  priority=int(a.get("priority", 0)), margin=float(a.get("margin", 0)), gap=float(a.get("gap", 0)),
                  solmix=float(a.get("solmix", 1)), group=int(a.get("group", 0)))
@@ -776,6 +814,22 @@ class _Compiler:
             if arr.ndim == 1 and key in ("size", "pos", "quat", "friction", "solref", "solimp"):
                 arr = arr.reshape(0, {"size": 3, "pos": 3, "quat": 4, "friction": 3, "solref": 2, "solimp": 5}[key])
             setattr(m, "geom_" + key, arr)
+        # convex hulls of the mesh geoms (mjModel: mesh_vertadr / mesh_vertnum / mesh_vert, geom_dataid)
+        mesh_ids, adr, num, verts = {}, [], [], []
+        dataid = np.full(len(G), -1, dtype=np.int32)
+        for gi, g in enumerate(G):
+            if g.get("mesh") is None:
+                continue
+            if g["mesh"] not in mesh_ids:
+                hv = self._mesh_props(g["mesh"])[4]
+                mesh_ids[g["mesh"]] = len(adr)
+                adr.append(sum(num)); num.append(len(hv)); verts.append(hv)
+            dataid[gi] = mesh_ids[g["mesh"]]
+        m.nmesh, m.nmeshvert = len(adr), int(sum(num))
+        m.mesh_vertadr = np.array(adr, dtype=np.int32)
+        m.mesh_vertnum = np.array(num, dtype=np.int32)
+        m.mesh_vert = np.concatenate(verts).reshape(-1, 3) if verts else np.zeros((0, 3))
+        m.geom_dataid = dataid
         m.nsite = len(S)
         m.names_site = np.array([s["name"] for s in S])
         m.site_bodyid = np.array([s["bodyid"] for s in S], dtype=np.int32)

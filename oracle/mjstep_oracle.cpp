@@ -332,6 +332,7 @@ template <typename T> void muscleGainBias(T len, T vel, const double* lr, T acc0
 // ------------------------------------------------------------------------------------------ convex support + MPR
 template <typename T> struct Shape {
   int type; V3<T> pos; const T* mat; V3<T> size; T margin;  // margin: inflation added along the query direction
+  const double* verts = nullptr; int nvert = 0;              // convex hull of a mesh geom (geom frame), mjModel.mesh_vert
 };
 template <typename T> V3<T> support(const Shape<T>& s, V3<T> dir) {  // dir: unit, world frame
   V3<T> d = mulMT(s.mat, dir), r{0, 0, 0};
@@ -349,6 +350,14 @@ template <typename T> V3<T> support(const Shape<T>& s, V3<T> dir) {  // dir: uni
       r.z = d.z >= 0 ? s.size.y : -s.size.y;
     } break;
     case G_BOX: r = {d.x >= 0 ? s.size.x : -s.size.x, d.y >= 0 ? s.size.y : -s.size.y, d.z >= 0 ? s.size.z : -s.size.z}; break;
+    case G_MESH: {  // support vertex of the convex hull (MuJoCo: hill climbing on the hull graph, mjc_meshSupport; same vertex)
+      T best = T(-1e300);
+      for (int i = 0; i < s.nvert; i++) {
+        V3<T> v{T(s.verts[3 * i]), T(s.verts[3 * i + 1]), T(s.verts[3 * i + 2])};
+        T val = dot(v, d);
+        if (val > best) { best = val; r = v; }
+      }
+    } break;
     default: break;
   }
   return mulM(s.mat, r) + s.pos + dir * s.margin;
@@ -800,6 +809,11 @@ template <typename T> struct Oracle {
     T dist = n - r1 - r2;
     addContact(g1, g2, pp, dist, c1 + nrm * (r1 + dist / 2), nrm);
   }
+  void meshOf(int g, Shape<T>& s) const {
+    if (m.geom_type[g] != G_MESH) return;
+    const int id = m.geom_dataid[g];
+    s.verts = m.mesh_vert + 3 * m.mesh_vertadr[id]; s.nvert = m.mesh_vertnum[id];
+  }
   void collidePair(int g1, int g2, const PairParam& pp) {
     int t1 = m.geom_type[g1], t2 = m.geom_type[g2];
     if (t1 > t2) { std::swap(g1, g2); std::swap(t1, t2); }
@@ -809,7 +823,7 @@ template <typename T> struct Oracle {
     T rb1 = T(m.geom_rbound[g1]), rb2 = T(m.geom_rbound[g2]);
     V3<T> ax1{R1[2], R1[5], R1[8]}, ax2{R2[2], R2[5], R2[8]};
     if (t1 == G_PLANE) {
-      if (t2 == G_PLANE || t2 == G_HFIELD || t2 == G_MESH) return;
+      if (t2 == G_PLANE || t2 == G_HFIELD) return;
       T cd = dot(p2 - p1, ax1);
       if (cd > rb2 + pp.margin) return;  // bounding-sphere cull
       auto planeSphere = [&](V3<T> c, T r) {
@@ -833,15 +847,17 @@ template <typename T> struct Oracle {
           cnt++;
         }
       }
-      else {  // ellipsoid, cylinder: deepest support point along -normal (single contact)
+      else {  // ellipsoid, cylinder, mesh hull: deepest support point along -normal (single contact; MuJoCo's mjc_PlaneConvex adds
+              // up to three more hull vertices near the plane for a mesh -- a documented difference)
         Shape<T> s{t2, p2, R2, sz2, 0};
+        meshOf(g2, s);
         V3<T> sp = support(s, ax1 * T(-1));
         T dist = dot(sp - p1, ax1);
         addContact(g1, g2, pp, dist, sp - ax1 * (dist / 2), ax1);
       }
       return;
     }
-    if (t1 == G_HFIELD || t2 == G_MESH || t1 == G_MESH) return;
+    if (t1 == G_HFIELD) return;
     if (norm(p2 - p1) > rb1 + rb2 + pp.margin) return;  // bounding-sphere cull
     if (t1 == G_SPHERE && t2 == G_SPHERE) { sphereSphere(g1, g2, pp, p1, sz1.x, p2, sz2.x); return; }
     if (t1 == G_SPHERE && t2 == G_CAPSULE) {
@@ -867,6 +883,7 @@ template <typename T> struct Oracle {
     }
     // general convex pair: MPR on shapes inflated by margin/2 each
     Shape<T> A{t1, p1, R1, sz1, pp.margin / 2}, B{t2, p2, R2, sz2, pp.margin / 2};
+    meshOf(g1, A); meshOf(g2, B);
     T depth; V3<T> nrm, pos;
     if (mprPenetration(A, B, T(1e-6), 50, &depth, &nrm, &pos)) addContact(g1, g2, pp, pp.margin - depth, pos, nrm);
   }
